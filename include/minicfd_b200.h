@@ -1,0 +1,188 @@
+/* minicfd_b200.h — C ABI of libminicfd_b200.so
+ *
+ * B200-native (sm_100a) implementation of miniCFD's per-Runge-Kutta-stage spatial residual
+ * (volume flux divergence + face Riemann flux + lifting) and the explicit RK update that
+ * consumes it, on Hexahedron8 meshes with nodal Lobatto expansions, FP64 throughout.
+ *
+ * The reference has no C ABI: its seam is a set of C++ templates.  Every
+ * entry point below therefore cites the reference member function(s) it stands in for; the header
+ * shim under include/mini/ keeps the reference's template names and forwards to these calls.
+ * Paths are relative to the reference repository root (pvcStillinGradSchool/miniCFD @ e14f896).
+ *
+ * Conventions: plain pointers and sizes only; every call returns 0 on success or a negative
+ * mcfd_status, never throws; mcfd_last_error() gives the message.  All calls for one context come
+ * from one host thread (the reference is single-threaded per MPI rank).  Kernels run on the stream
+ * given by mcfd_set_stream (default: the legacy default stream).  There is NO CPU fallback: every
+ * compute entry point fails with MCFD_ERR_CUDA when no usable device is present.
+ *
+ * Column layout = the reference's: column[cell_id * kFields + node * K + component], node index
+ * ijk = (i*Q + j)*Q + k (include/mini/mesh/part.hpp:755-759,784-787;
+ * include/mini/polynomial/hexahedron.hpp:662-677; include/mini/basis/lagrange.hpp:239-253), K = 5,
+ * kFields = 5*(P+1)^3.  On the device the state lives in coefficient-major tiles of 32 cells
+ * (DESIGN.md section 3); the entry points convert.
+ */
+#ifndef MINICFD_B200_H_
+#define MINICFD_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mcfd_ctx mcfd_ctx;
+
+typedef enum {
+  MCFD_OK = 0,
+  MCFD_ERR_ARG = -1,     /* invalid argument / unsupported configuration */
+  MCFD_ERR_CUDA = -2,    /* CUDA runtime failure, including "no device" */
+  MCFD_ERR_MESH = -3,    /* inconsistent mesh description */
+  MCFD_ERR_STATE = -4    /* call sequence error (e.g. no mesh yet) */
+} mcfd_status;
+
+/* Spatial scheme: include/mini/spatial/fr/lobatto.hpp:36-434 (Huynh-lumped FR on Lobatto points)
+ * or include/mini/spatial/dg/lobatto.hpp:32-303 (DGSEM). */
+typedef enum { MCFD_FR_LOBATTO = 0, MCFD_DG_LOBATTO = 1 } mcfd_scheme;
+
+/* Riemann solver behind mini::riemann::rotated::Euler<...> (include/mini/riemann/rotated/euler.hpp:
+ * 153-159): include/mini/riemann/euler/exact.hpp:44-46, hllc.hpp:30-44, ausm.hpp:30-33. */
+typedef enum { MCFD_EXACT = 0, MCFD_HLLC = 1, MCFD_AUSM = 2 } mcfd_riemann;
+
+/* Boundary kinds: the seven Set* methods of include/mini/spatial/fem.hpp:196-222; fluxes from
+ * include/mini/riemann/rotated/euler.hpp:144-174, 181-236, 260-280, 296-299.  MCFD_BC_NO_SLIP_WALL is
+ * a no-op for inviscid Riemann types (fem.hpp:382-383), as in the reference. */
+typedef enum {
+  MCFD_BC_INVISCID_WALL = 0,
+  MCFD_BC_SUPERSONIC_OUTLET = 1,
+  MCFD_BC_SUPERSONIC_INLET = 2,
+  MCFD_BC_SUBSONIC_INLET = 3,
+  MCFD_BC_SUBSONIC_OUTLET = 4,
+  MCFD_BC_SMART = 5,
+  MCFD_BC_NO_SLIP_WALL = 6
+} mcfd_bc_kind;
+
+typedef struct {
+  int32_t scheme;    /* mcfd_scheme */
+  int32_t degree;    /* P: 2 or 3 (template parameter kDegrees, demo/euler/sourceless.hpp:27) */
+  int32_t riemann;   /* mcfd_riemann */
+  int32_t device;    /* CUDA device ordinal, -1 = current device */
+} mcfd_config;
+
+/* -- life cycle ------------------------------------------------------------------------------ */
+
+/* Replaces: `Spatial spatial(&part)` (demo/euler/sourceless.cpp:120) as far as device resources
+ * go.  gamma is fixed to 1.4 like `IdealGas<Scalar, 1.4>` in demo/euler/sourceless.hpp:21. */
+int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out);
+int mcfd_destroy(mcfd_ctx *ctx);
+const char *mcfd_last_error(const mcfd_ctx *ctx);   /* ctx may be NULL: last create() error */
+/* Kernels and copies of this context run on `cuda_stream` (a cudaStream_t passed as void*). */
+int mcfd_set_stream(mcfd_ctx *ctx, void *cuda_stream);
+
+/* -- Part / Cell / Face storage (include/mini/mesh/part.hpp:97-291, 404-445, 932-1019, 1456-1549) */
+
+/* Describe one part.  Cells [0,n_local) are local in the part's own id order (inner cells first,
+ * then inter cells, part.hpp:746-767), cells [n_local, n_local+n_ghost) are ghosts (part.hpp:768-
+ * 775).  cell_nodes: [n_cells][8] node ids in CGNS HEXA_8 order
+ * (include/mini/coordinate/hexahedron.hpp:378-389).  Interior faces are found by shared node sets
+ * (part.hpp:939-966); bface_nodes [n_bfaces][4] name the boundary quads, bface_tags their section.
+ * periodic_pairs [n_pairs][2][4] optionally identifies quads (vertex m of the first with vertex m of
+ * the second) — no counterpart in the reference, which has no periodic boundary. */
+int mcfd_set_mesh(mcfd_ctx *ctx, int64_t n_nodes, const double *xyz,
+                  int64_t n_local, int64_t n_ghost, const int64_t *cell_nodes,
+                  int64_t n_bfaces, const int64_t *bface_nodes, const int32_t *bface_tags,
+                  int64_t n_pairs, const int64_t *periodic_pairs);
+
+/* Connectivity as the reference numbers it.  kind: 0 local, 1 ghost, 2 boundary faces
+ * (part.hpp:115).  Any output pointer may be NULL.  holder/sharer are cell ids (sharer = -1 on
+ * boundaries), holder_face/sharer_face local face ids 0..5, orientation the vertex correspondence
+ * code.  Returns the number of faces of that kind. */
+int64_t mcfd_get_faces(const mcfd_ctx *ctx, int kind, int64_t *holder, int64_t *sharer,
+                       int32_t *holder_face, int32_t *sharer_face, int32_t *orientation);
+/* Cell::length() and Cell::volume() (part.hpp:230, 239-244) of the local cells. */
+int mcfd_get_cell_geometry(const mcfd_ctx *ctx, double *length, double *volume);
+
+/* Halo lists: Part::send_cell_ptrs_/recv_cell_ptrs_ (part.hpp:904-931, 1435-1438).  `cells` are
+ * cell ids in pack order; the wire format per cell is the reference's kFields doubles
+ * (include/mini/polynomial/expansion.hpp:83-90). */
+int mcfd_set_halo(mcfd_ctx *ctx, int32_t n_send_parts, const int64_t *send_counts,
+                  const int64_t *send_cells, int32_t n_recv_parts, const int64_t *recv_counts,
+                  const int64_t *recv_cells);
+/* Device buffers of the packed halo (all neighbours back to back, in list order). */
+int mcfd_halo_buffers(mcfd_ctx *ctx, double **send_dev, int64_t *send_doubles,
+                      double **recv_dev, int64_t *recv_doubles);
+/* Part::ShareGhostCellCoeffs (part.hpp:1273-1278) up to, not including, MPI_Isend: pack the
+ * current solution of the send cells into the send buffer. */
+int mcfd_halo_pack(mcfd_ctx *ctx);
+/* Part::UpdateGhostCellCoeffs (part.hpp:1309-1314) after MPI_Waitall: unpack the recv buffer into
+ * the ghost cells of the current solution. */
+int mcfd_halo_unpack(mcfd_ctx *ctx);
+
+/* -- boundary conditions (fem.hpp:71-74, 196-222) -------------------------------------------- */
+
+int mcfd_set_boundary(mcfd_ctx *ctx, int32_t tag, int32_t bc_kind);
+/* Number of boundary faces carrying `tag`, in the order of the boundary face table. */
+int64_t mcfd_count_boundary_faces(const mcfd_ctx *ctx, int32_t tag);
+/* Flux-point coordinates [face][Q*Q][3] at which the reference evaluates its
+ * std::function<Value(Global const&, double)> (fr/lobatto.hpp:350, 373, 396, 419). */
+int mcfd_get_boundary_points(const mcfd_ctx *ctx, int32_t tag, double *xyz);
+/* The pre-sampled values of that function, [face][Q*Q][5], host pointer. */
+int mcfd_set_boundary_values(mcfd_ctx *ctx, int32_t tag, const double *values);
+/* Called with the stage time before every residual evaluation inside mcfd_rk_step, so that
+ * time-dependent boundary functions can be re-sampled (fem.hpp:225-227 SetTime). */
+typedef void (*mcfd_time_callback)(void *user, double t);
+int mcfd_set_time_callback(mcfd_ctx *ctx, mcfd_time_callback fn, void *user);
+
+/* -- temporal::System interface (include/mini/temporal/ode.hpp:17-48) -------------------------- */
+
+int64_t mcfd_count_local_cells(const mcfd_ctx *ctx);
+int64_t mcfd_cell_data_size(const mcfd_ctx *ctx);          /* Part::GetCellDataSize, part.hpp:793 */
+/* FiniteElement::SetSolutionColumn / GetSolutionColumn (fem.hpp:228-247); host pointers. */
+int mcfd_set_solution(mcfd_ctx *ctx, const double *column);
+int mcfd_get_solution(mcfd_ctx *ctx, double *column);
+/* Same with device pointers (column layout, kFields*n_local doubles). */
+int mcfd_set_solution_device(mcfd_ctx *ctx, const double *column_dev);
+int mcfd_get_solution_device(mcfd_ctx *ctx, double *column_dev);
+/* FiniteElement::GetResidualColumn (fem.hpp:248-258; fr/general.hpp:249-268; dg/lobatto.hpp:143-
+ * 158) at time t for the current solution; ghost cells must be current (mcfd_halo_unpack).
+ * column: host pointer or NULL; column_dev: device pointer or NULL. */
+int mcfd_residual(mcfd_ctx *ctx, double t, double *column, double *column_dev);
+
+/* -- temporal::RungeKutta (include/mini/temporal/rk.hpp:16-56) --------------------------------- */
+
+/* One full RungeKutta<order>::Update(system, t, dt) for a part without ghosts (or whose ghosts the
+ * caller does not need to refresh), fused: each stage is one kernel that evaluates the residual and
+ * writes the next stage state.  order = 1, 2 or 3. */
+int mcfd_rk_step(mcfd_ctx *ctx, int order, double t, double dt);
+/* The same, stage by stage, for parts with ghost cells:
+ *   mcfd_rk_begin; for s in 0..order-1 { mcfd_halo_pack; <exchange>; mcfd_rk_stage_inner(s);
+ *   mcfd_halo_unpack; mcfd_rk_stage_inter(s); }
+ * stage_inner advances the tiles holding only inner cells (no ghost neighbour) and can overlap the
+ * exchange, stage_inter the rest — the overlap of fem.hpp:249-256. */
+int mcfd_rk_begin(mcfd_ctx *ctx, int order, double t, double dt);
+int mcfd_rk_stage_inner(mcfd_ctx *ctx, int stage);
+int mcfd_rk_stage_inter(mcfd_ctx *ctx, int stage);
+/* Time of the residual evaluation of `stage` in the step opened by mcfd_rk_begin. */
+double mcfd_rk_stage_time(const mcfd_ctx *ctx, int stage);
+
+/* FiniteElement::GetTimeStep (fem.hpp:411-435) incl. the FR-Lobatto doubling
+ * (fr/lobatto.hpp:220-222): the part-local value, before MPI_Allreduce(MIN)
+ * (demo/euler/sourceless.cpp:191-194). */
+int mcfd_time_step(mcfd_ctx *ctx, double dt_guess, int rk_order, double *dt_local);
+
+/* -- diagnostics --------------------------------------------------------------------------------- */
+
+/* Number of kernels this context has launched so far (bench.py's gpu_launches). */
+int64_t mcfd_launch_count(const mcfd_ctx *ctx);
+/* Duration in ms of the stage kernels launched since the last call with reset != 0, measured with
+ * CUDA events on the context's stream when timing is enabled (bench.py's roofline leg). */
+int mcfd_enable_kernel_timing(mcfd_ctx *ctx, int enable);
+int mcfd_kernel_time(mcfd_ctx *ctx, double *total_ms, int64_t *n_launches, int reset);
+/* One rotated Riemann problem on the device (test hook): frame normal n[3], conservative states,
+ * bc_kind < 0 for an interior face. */
+int mcfd_riemann_flux(mcfd_ctx *ctx, int32_t bc_kind, int64_t n, const double *normals,
+                      const double *u_left, const double *u_right, double *flux);
+
+#ifdef __cplusplus
+}
+#endif
+#endif  /* MINICFD_B200_H_ */

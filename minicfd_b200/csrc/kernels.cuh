@@ -1,0 +1,368 @@
+// kernels.cuh — device data layout and kernels of libminicfd_b200 (sm_100a).
+//
+// Layout ("tiles"): cells are grouped 32 at a time; within a tile every scalar is stored as a row of
+// 32 doubles, one per cell, so a warp whose lanes are the 32 cells of a tile reads and writes whole
+// 256-byte rows:
+//     U   [tile][node*5 + component][lane]     solution coefficients (kFields rows per tile)
+//     G   [tile][21][lane]                     trilinear map coefficients c1..c7 (3 doubles each)
+//     NBR [tile][6][lane]  int32               neighbour cell id across local face f, or -1-b for
+//                                              boundary face b
+//     CODE[tile][6][lane]  uint8               sharer face | orientation<<3 | i_am_holder<<6
+// Ghost cells are ordinary cells appended after the local ones.
+#ifndef MINICFD_B200_KERNELS_CUH_
+#define MINICFD_B200_KERNELS_CUH_
+
+#include <cstdint>
+
+#include "physics.cuh"
+
+namespace mcfd {
+
+constexpr int kTile = 32;       // cells per tile
+constexpr int kGeomRows = 21;   // c1..c7, xyz each
+constexpr int kMaxQ = 4;
+constexpr int kMaxN = kMaxQ * kMaxQ * kMaxQ;
+constexpr int kMaxFaceQ = kMaxQ * kMaxQ;
+constexpr int kMaxSlots = 8;    // node slots per warp
+constexpr int kMaxWarps = 16;
+
+// Per-degree tables, filled by the host (tables.cpp) and copied to constant memory.
+struct Tables {
+  double xi[kMaxQ];                    // Lobatto points (integrator/lobatto.hpp:38-57)
+  double a[kMaxQ][kMaxQ];              // R[c] += a[i][m] * Fhat_d(node m on the d-line)[c]
+  double coef_f;                       // R -= coef_f * |n| * f_upwind
+  double coef_F;                       // R += coef_F * sgn * Fhat_d   (0 for DG)
+  int slot_node[kMaxWarps * kMaxSlots];  // node handled by (warp, slot), -1 = idle
+  // face-point index q of node n on its face in direction d (or -1 when not on a face)
+  signed char node_q[kMaxN][3];
+  // neighbour node for (sharer face f', orientation o, my face-point q)
+  unsigned char nbr_node[6][8][kMaxFaceQ];
+};
+
+struct StageArgs {
+  const double *u_in;     // stage state (tiles, incl. ghosts)
+  const double *u0;       // state at the beginning of the step (tiles)
+  double *u_out;          // next stage state, or the residual when mode == kModeResidual
+  const double *geom;
+  const int *nbr;
+  const unsigned char *code;
+  const unsigned char *bkind;   // [n_bfaces] boundary kind
+  const double *bvals;          // [n_bfaces][Q*Q][5] pre-sampled boundary function
+  int n_local;                  // cells [0, n_local) are advanced
+  int block_begin;              // first CTA-sized cell block of this launch
+  int mode;
+  double dt;
+};
+
+enum : int {
+  kModeResidual = 0,  // out = R
+  kModeEuler = 1,     // out = u + R*dt                        (ode.hpp:121-133)
+  kModeRk3b = 2,      // out = (u0*3 + (u + R*dt)) / 4         (rk.hpp:36-40)
+  kModeRk3c = 3,      // out = ((u + R*dt)*2 + u0) / 3         (rk.hpp:42-47)
+  kModeRk2b = 4       // out = ((u + R*dt) + u0) * 0.5         (rk.hpp:24-29)
+};
+
+MCFD_CONSTANT Tables c_tab;
+
+// Rows r0,r1,r2 of the Jacobian J = d(x,y,z)/d(xi,eta,zeta) of the trilinear map at (x,e,z)
+// (coordinate/hexahedron.hpp:431-456, element.hpp:44-47) from the coefficient rows in `g`
+// (stride `gs` doubles between rows), then J* = det(J) J^-1 by cofactors
+// (polynomial/hexahedron.hpp:221-231): column d of J* is the cross product of the other two rows.
+struct Metric {
+  double s[3][3];  // s[d][x] = J*(x, d): the (unnormalised) normal of the d-faces
+  double det;
+};
+
+MCFD_HD Metric ComputeMetric(const double *g, int gs, double x, double e, double z) {
+  double r[3][3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    double c1 = g[(0 + k) * gs], c2 = g[(3 + k) * gs], c3 = g[(6 + k) * gs];
+    double c4 = g[(9 + k) * gs], c5 = g[(12 + k) * gs], c6 = g[(15 + k) * gs], c7 = g[(18 + k) * gs];
+    r[0][k] = fma(z, fma(e, c7, c6), fma(e, c4, c1));
+    r[1][k] = fma(z, fma(x, c7, c5), fma(x, c4, c2));
+    r[2][k] = fma(e, fma(x, c7, c5), fma(x, c6, c3));
+  }
+  Metric m;
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    const double *a = r[(d + 1) % 3], *b = r[(d + 2) % 3];
+    m.s[d][0] = a[1] * b[2] - a[2] * b[1];
+    m.s[d][1] = a[2] * b[0] - a[0] * b[2];
+    m.s[d][2] = a[0] * b[1] - a[1] * b[0];
+  }
+  m.det = r[0][0] * m.s[0][0] + r[0][1] * m.s[0][1] + r[0][2] * m.s[0][2];
+  return m;
+}
+
+// One RK stage (or a bare residual) for the cells of a CTA-sized block.
+//   CPB  cells per CTA: 32 (a whole tile, one node per warp at a time) or 16 (half a tile, two
+//        nodes per warp at a time) — bounded by the shared-memory flux cache of N*15*CPB doubles.
+//   NW   warps per CTA.
+// The body is written as per-thread phase functions of (thread id, block id, shared memory) so that
+// tests/host_emulation can run the very same source on the host to debug index logic without a GPU;
+// the __global__ kernel below strings them together with __syncthreads().
+template <int Q, int CPB, int NW>
+struct StageGeometry {
+  static constexpr int N = Q * Q * Q;
+  static constexpr int F = 5 * N;
+  static constexpr int FQ = Q * Q;
+  static constexpr int SUB = kTile / CPB;                 // nodes handled at once by a warp
+  static constexpr int SLOTS = (N + NW * SUB - 1) / (NW * SUB);
+  static constexpr size_t kSharedBytes =
+      (size_t)(N * 15 * CPB + kGeomRows * CPB) * sizeof(double) + 6 * 8 * FQ;
+  int lane, warp, lc, sub, block, tile, tl, cell;
+  bool active;
+  double *sF, *sG;
+  unsigned char *sNbrNode;
+  MCFD_HD StageGeometry(const StageArgs &p, int tid, int bid, double *smem) {
+    sF = smem;                                      // [N][15][CPB]
+    sG = smem + N * 15 * CPB;                       // [21][CPB]
+    sNbrNode = reinterpret_cast<unsigned char *>(sG + kGeomRows * CPB);  // [6][8][FQ]
+    lane = tid & 31; warp = tid >> 5;
+    lc = lane % CPB;                                // cell within the block
+    sub = lane / CPB;
+    block = p.block_begin + bid;
+    tile = block / SUB;
+    tl = (block % SUB) * CPB + lc;                  // lane within the tile
+    cell = tile * kTile + tl;
+    active = cell < p.n_local;
+  }
+  MCFD_HD int Node(int s) const {
+    int slot = (warp * SLOTS + s) * SUB + sub;
+    return (slot < kMaxWarps * kMaxSlots) ? c_tab.slot_node[slot] : -1;
+  }
+};
+
+template <int Q, int CPB, int NW>
+MCFD_HD void StagePrologue(const StageArgs &p, int tid, int bid, double *smem) {
+  StageGeometry<Q, CPB, NW> g(p, tid, bid, smem);
+  constexpr int FQ = Q * Q;
+  for (int i = tid; i < 6 * 8 * FQ; i += NW * 32) {
+    g.sNbrNode[i] = c_tab.nbr_node[i / (8 * FQ)][(i / FQ) % 8][i % FQ];
+  }
+  for (int i = tid; i < kGeomRows * CPB; i += NW * 32) {
+    int row = i / CPB, c = i % CPB;
+    g.sG[i] = p.geom[((size_t)g.tile * kGeomRows + row) * kTile + (g.block % g.SUB) * CPB + c];
+  }
+}
+
+// ---- phase A: contravariant fluxes Fhat = F(u) J* at every node -> shared memory --------------
+// (fr/general.hpp:276-279; fem.hpp:392-395; types.hpp:322-333; polynomial/hexahedron.hpp:607-611)
+template <int Q, int CPB, int NW>
+MCFD_HD void StagePhaseA(const StageArgs &p, int tid, int bid, double *smem) {
+  using G = StageGeometry<Q, CPB, NW>;
+  G g(p, tid, bid, smem);
+  constexpr int F = G::F, FQ = G::FQ;
+  const double *uin = p.u_in + (size_t)g.tile * F * kTile + g.tl;
+#pragma unroll 1
+  for (int s = 0; s < G::SLOTS; ++s) {
+    int n = g.Node(s);
+    if (n < 0) continue;
+    int i = n / FQ, j = (n / Q) % Q, k = n % Q;
+    double u[5];
+#pragma unroll
+    for (int c = 0; c < 5; ++c) u[c] = uin[(n * 5 + c) * kTile];
+    Prim q = ConsToPrim(u[0], u[1], u[2], u[3], u[4]);
+    Metric m = ComputeMetric(g.sG + g.lc, CPB, c_tab.xi[i], c_tab.xi[j], c_tab.xi[k]);
+    double h0 = u[4] + q.p;
+    double vel[3] = {q.u, q.v, q.w};
+    double fx[3][5];  // flux matrix columns (x, y, z)
+#pragma unroll
+    for (int x = 0; x < 3; ++x) {
+      fx[x][0] = u[1 + x];
+      fx[x][1] = u[1] * vel[x];
+      fx[x][2] = u[2] * vel[x];
+      fx[x][3] = u[3] * vel[x];
+      fx[x][1 + x] += q.p;
+      fx[x][4] = h0 * vel[x];
+    }
+    double *dst = g.sF + (size_t)n * 15 * CPB + g.lc;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+#pragma unroll
+      for (int c = 0; c < 5; ++c) {
+        dst[(d * 5 + c) * CPB] = fx[0][c] * m.s[d][0] + fx[1][c] * m.s[d][1] + fx[2][c] * m.s[d][2];
+      }
+    }
+  }
+}
+
+// ---- phase B: divergence + face corrections + 1/det + RK update --------------------------------
+template <int Q, int kRiemann, int CPB, int NW>
+MCFD_HD void StagePhaseB(const StageArgs &p, int tid, int bid, double *smem) {
+  using G = StageGeometry<Q, CPB, NW>;
+  G g(p, tid, bid, smem);
+  constexpr int F = G::F, FQ = G::FQ;
+  if (!g.active) return;
+  const int tile = g.tile, tl = g.tl, lc = g.lc;
+  const double *uin = p.u_in + (size_t)tile * F * kTile + tl;
+#pragma unroll 1
+  for (int s = 0; s < G::SLOTS; ++s) {
+    int n = g.Node(s);
+    if (n < 0) continue;
+    int ijk[3] = {n / FQ, (n / Q) % Q, n % Q};
+    const int stride[3] = {FQ, Q, 1};
+    double r[5] = {0, 0, 0, 0, 0};
+    // flux divergence along the three node lines (fr/general.hpp:280-286; dg/lobatto.hpp:161-170)
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      int base = n - ijk[d] * stride[d];
+#pragma unroll
+      for (int mm = 0; mm < Q; ++mm) {
+        double a = c_tab.a[ijk[d]][mm];
+        const double *src = g.sF + ((size_t)(base + mm * stride[d]) * 15 + d * 5) * CPB + lc;
+#pragma unroll
+        for (int c = 0; c < 5; ++c) r[c] = fma(a, src[c * CPB], r[c]);
+      }
+    }
+    double u[5];
+#pragma unroll
+    for (int c = 0; c < 5; ++c) u[c] = uin[(n * 5 + c) * kTile];
+    Metric m = ComputeMetric(g.sG + lc, CPB, c_tab.xi[ijk[0]], c_tab.xi[ijk[1]], c_tab.xi[ijk[2]]);
+    // face corrections (fr/lobatto.hpp:232-251, 278-428; fr/general.hpp:296-315; dg/lobatto.hpp:171-191)
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      int q = c_tab.node_q[n][d];
+      if (q < 0) continue;
+      const bool plus = ijk[d] != 0;               // faces 2,3,5 are the +1 sides
+      const int f = (d == 0) ? (plus ? 2 : 4) : (d == 1) ? (plus ? 3 : 1) : (plus ? 5 : 0);
+      const int nb = p.nbr[((size_t)tile * 6 + f) * kTile + tl];
+      const double sgn = plus ? 1.0 : -1.0;
+      double nx = m.s[d][0], ny = m.s[d][1], nz = m.s[d][2];
+      double area = sqrt(nx * nx + ny * ny + nz * nz);
+      double inv = sgn / area;
+      nx *= inv; ny *= inv; nz *= inv;             // outward unit normal
+      double fl[5];
+      if (nb >= 0) {
+        const int code = p.code[((size_t)tile * 6 + f) * kTile + tl];
+        const int n2 = g.sNbrNode[((code & 7) * 8 + ((code >> 3) & 7)) * FQ + q];
+        const double *src = p.u_in + ((size_t)(nb >> 5) * F + n2 * 5) * kTile + (nb & 31);
+        double v[5];
+#pragma unroll
+        for (int c = 0; c < 5; ++c) v[c] = src[c * kTile];
+        if (code & 64) {  // I hold this face: normal points from me to the neighbour
+          FluxUpwind<kRiemann>(u, v, nx, ny, nz, fl);
+        } else {          // evaluate in the holder's frame, as the reference does
+          FluxUpwind<kRiemann>(v, u, -nx, -ny, -nz, fl);
+#pragma unroll
+          for (int c = 0; c < 5; ++c) fl[c] = -fl[c];
+        }
+      } else {
+        const int b = -1 - nb;
+        const int kind = p.bkind[b];
+        if (kind == kBcNoSlip) continue;
+        BoundaryFlux<kRiemann>(kind, u, p.bvals + ((size_t)b * FQ + q) * 5, nx, ny, nz, fl);
+      }
+      const double cf = c_tab.coef_f * area, cF = c_tab.coef_F * sgn;
+      const double *own = g.sF + ((size_t)n * 15 + d * 5) * CPB + lc;
+#pragma unroll
+      for (int c = 0; c < 5; ++c) r[c] = fma(cF, own[c * CPB], fma(-cf, fl[c], r[c]));
+    }
+    const double inv_det = 1.0 / m.det;            // fr/general.hpp:256-266; dg/lobatto.hpp:143-158
+    double *out = p.u_out + (size_t)tile * F * kTile + tl;
+    const double *u0 = p.u0 + (size_t)tile * F * kTile + tl;
+#pragma unroll
+    for (int c = 0; c < 5; ++c) {
+      double res = r[c] * inv_det;
+      double val;
+      switch (p.mode) {
+      case kModeResidual: val = res; break;
+      case kModeEuler: val = u[c] + res * p.dt; break;
+      case kModeRk3b: val = (u0[(n * 5 + c) * kTile] * 3 + (u[c] + res * p.dt)) * 0.25; break;
+      case kModeRk3c: val = ((u[c] + res * p.dt) * 2 + u0[(n * 5 + c) * kTile]) / 3; break;
+      default: val = ((u[c] + res * p.dt) + u0[(n * 5 + c) * kTile]) * 0.5; break;
+      }
+      out[(n * 5 + c) * kTile] = val;
+    }
+  }
+}
+
+#ifdef __CUDACC__
+template <int Q, int kRiemann, int CPB, int NW>
+__global__ void __launch_bounds__(NW * 32, (Q == 3 ? 2 : 1))
+StageKernel(StageArgs p) {
+  extern __shared__ double smem[];
+  StagePrologue<Q, CPB, NW>(p, threadIdx.x, blockIdx.x, smem);
+  __syncthreads();
+  StagePhaseA<Q, CPB, NW>(p, threadIdx.x, blockIdx.x, smem);
+  __syncthreads();
+  StagePhaseB<Q, kRiemann, CPB, NW>(p, threadIdx.x, blockIdx.x, smem);
+}
+
+// FiniteElement::GetTimeStep's reduction (fem.hpp:417-432; rotated/euler.hpp:340-345): one thread per
+// cell, min over cells of length / max(1e-5, max_nodes(c + |v|)), folded into *result by atomicMin
+// on the bit pattern (valid for non-negative doubles).
+template <int Q>
+__global__ void TimeStepKernel(const double *u, const double *length, int n_local,
+    unsigned long long *result) {
+  constexpr int N = Q * Q * Q, F = 5 * N;
+  int cell = blockIdx.x * blockDim.x + threadIdx.x;
+  double dt = 1e100;
+  if (cell < n_local) {
+    const double *src = u + (size_t)(cell >> 5) * F * kTile + (cell & 31);
+    double vmax = 1e-5;
+    for (int n = 0; n < N; ++n) {
+      Prim q = ConsToPrim(src[(n * 5) * kTile], src[(n * 5 + 1) * kTile], src[(n * 5 + 2) * kTile],
+                          src[(n * 5 + 3) * kTile], src[(n * 5 + 4) * kTile]);
+      double c = SoundSpeed(q.rho, q.p);
+      double v = sqrt(q.u * q.u + q.v * q.v + q.w * q.w);
+      vmax = fmax(vmax, fmax(c + v, c - v));
+    }
+    dt = length[cell] / vmax;
+  }
+  for (int o = 16; o > 0; o >>= 1) dt = fmin(dt, __shfl_xor_sync(0xffffffffu, dt, o));
+  if ((threadIdx.x & 31) == 0) atomicMin(result, (unsigned long long)__double_as_longlong(dt));
+}
+
+// column[cell*F + f]  <->  tiles[(tile*F + f)*32 + lane]; one CTA per tile, staged through shared
+// memory so both sides are coalesced.  `cells` (optional) lists the cells to move (halo pack/unpack:
+// item i of the column is cell cells[i]).
+template <int F, bool kToTiles>
+__global__ void ConvertKernel(double *tiles, double *column, const int *cells, int n_items) {
+  constexpr int FP = F + 1;  // padded: conflict-free transposed access
+  extern __shared__ double sbuf[];  // [32][FP]
+  int first = blockIdx.x * kTile;
+  int count = min(kTile, n_items - first);
+  if (kToTiles) {
+    for (int i = threadIdx.x; i < count * F; i += blockDim.x)
+      sbuf[(i / F) * FP + i % F] = column[(size_t)first * F + i];
+    __syncthreads();
+    for (int i = threadIdx.x; i < F * kTile; i += blockDim.x) {
+      int f = i / kTile, l = i % kTile;
+      if (l < count) {
+        int cell = cells ? cells[first + l] : first + l;
+        tiles[((size_t)(cell >> 5) * F + f) * kTile + (cell & 31)] = sbuf[l * FP + f];
+      }
+    }
+  } else {
+    for (int i = threadIdx.x; i < F * kTile; i += blockDim.x) {
+      int f = i / kTile, l = i % kTile;
+      if (l < count) {
+        int cell = cells ? cells[first + l] : first + l;
+        sbuf[l * FP + f] = tiles[((size_t)(cell >> 5) * F + f) * kTile + (cell & 31)];
+      }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < count * F; i += blockDim.x)
+      column[(size_t)first * F + i] = sbuf[(i / F) * FP + i % F];
+  }
+}
+
+// Test hook: n independent rotated Riemann problems.
+template <int kRiemann>
+__global__ void RiemannKernel(int bc_kind, int n, const double *normals, const double *ul,
+    const double *ur, double *flux) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double a[5], b[5], f[5];
+  for (int c = 0; c < 5; ++c) { a[c] = ul[i * 5 + c]; b[c] = ur[i * 5 + c]; }
+  if (bc_kind < 0) FluxUpwind<kRiemann>(a, b, normals[3 * i], normals[3 * i + 1], normals[3 * i + 2], f);
+  else BoundaryFlux<kRiemann>(bc_kind, a, b, normals[3 * i], normals[3 * i + 1], normals[3 * i + 2], f);
+  for (int c = 0; c < 5; ++c) flux[i * 5 + c] = f[c];
+}
+
+#endif  // __CUDACC__
+
+}  // namespace mcfd
+#endif  // MINICFD_B200_KERNELS_CUH_

@@ -1,0 +1,641 @@
+// libmcfd.cu — the C ABI of include/minicfd_b200.h on top of kernels.cuh.
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "../../include/minicfd_b200.h"
+#include "kernels.cuh"
+#include "tables.hpp"
+
+using namespace mcfd;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+template <class T>
+struct DevBuf {
+  T *p = nullptr;
+  size_t n = 0;
+  cudaError_t Alloc(size_t count) {
+    Free();
+    n = count;
+    if (count == 0) return cudaSuccess;
+    return cudaMalloc(&p, count * sizeof(T));
+  }
+  void Free() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    n = 0;
+  }
+  ~DevBuf() { Free(); }
+};
+
+}  // namespace
+
+struct mcfd_ctx {
+  mcfd_config cfg{};
+  int q = 3, n_nodes = 27, fields = 135;
+  int cpb = 32, n_warps = 9;
+  cudaStream_t stream = nullptr;
+  std::string error;
+  Tables tables{};
+  HostMesh mesh;
+  bool has_mesh = false;
+  int64_t n_cells = 0, n_tiles = 0;
+  std::vector<int32_t> btag_of_face;           // per boundary face
+  std::vector<unsigned char> bkind_host;
+  std::map<int32_t, int32_t> tag_kind;
+  DevBuf<double> u[3], res, geom, bvals, length, column;
+  DevBuf<int> nbr, send_cells, recv_cells;
+  DevBuf<unsigned char> code, bkind;
+  DevBuf<double> send_buf, recv_buf;
+  DevBuf<unsigned long long> dt_bits;
+  int cur = 0;                                  // index of the current solution in u[]
+  // open RK step
+  int rk_order = 0, rk_u0 = 0, rk_in = 0;
+  double rk_t = 0, rk_dt = 0;
+  mcfd_time_callback time_cb = nullptr;
+  void *time_user = nullptr;
+  int64_t launches = 0;
+  // kernel timing
+  bool timing = false;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> events;
+  size_t events_used = 0;
+  int64_t inner_blocks = 0, total_blocks = 0;  // CTA-sized blocks without / with ghost neighbours
+};
+
+namespace {
+
+int Fail(mcfd_ctx *ctx, int status, std::string msg) {
+  if (ctx) ctx->error = std::move(msg);
+  else g_create_error = std::move(msg);
+  return status;
+}
+
+#define MCFD_CUDA(ctx, call)                                                          \
+  do {                                                                                \
+    cudaError_t e_ = (call);                                                          \
+    if (e_ != cudaSuccess)                                                            \
+      return Fail(ctx, MCFD_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+  } while (0)
+
+template <int Q, int R, int CPB, int NW>
+cudaError_t LaunchStageT(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
+  size_t smem = StageGeometry<Q, CPB, NW>::kSharedBytes;
+  auto kernel = StageKernel<Q, R, CPB, NW>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  kernel<<<n_blocks, NW * 32, smem, ctx->stream>>>(a);
+  return cudaGetLastError();
+}
+
+template <int Q, int CPB, int NW>
+cudaError_t LaunchStageQ(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
+  switch (ctx->cfg.riemann) {
+  case MCFD_EXACT: return LaunchStageT<Q, kExact, CPB, NW>(ctx, a, n_blocks);
+  case MCFD_HLLC: return LaunchStageT<Q, kHllc, CPB, NW>(ctx, a, n_blocks);
+  default: return LaunchStageT<Q, kAusm, CPB, NW>(ctx, a, n_blocks);
+  }
+}
+
+// Launch the stage kernel over CTA blocks [block_begin, block_end).
+int LaunchStage(mcfd_ctx *ctx, const double *u_in, const double *u0, double *u_out, int mode,
+    double dt, int64_t block_begin, int64_t block_end) {
+  if (block_end <= block_begin) return MCFD_OK;
+  StageArgs a;
+  a.u_in = u_in; a.u0 = u0; a.u_out = u_out;
+  a.geom = ctx->geom.p; a.nbr = ctx->nbr.p; a.code = ctx->code.p;
+  a.bkind = ctx->bkind.p; a.bvals = ctx->bvals.p;
+  a.n_local = (int)ctx->mesh.n_local;
+  a.block_begin = (int)block_begin;
+  a.mode = mode; a.dt = dt;
+  int n_blocks = (int)(block_end - block_begin);
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (ctx->timing) {
+    if (ctx->events_used == ctx->events.size()) {
+      cudaEvent_t a0, a1;
+      MCFD_CUDA(ctx, cudaEventCreate(&a0));
+      MCFD_CUDA(ctx, cudaEventCreate(&a1));
+      ctx->events.emplace_back(a0, a1);
+    }
+    e0 = ctx->events[ctx->events_used].first;
+    e1 = ctx->events[ctx->events_used].second;
+    ctx->events_used++;
+    MCFD_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
+  }
+  cudaError_t e = (ctx->q == 3) ? LaunchStageQ<3, 32, 9>(ctx, a, n_blocks)
+                                : LaunchStageQ<4, 16, 16>(ctx, a, n_blocks);
+  if (e != cudaSuccess) return Fail(ctx, MCFD_ERR_CUDA, std::string("stage kernel: ") + cudaGetErrorString(e));
+  if (ctx->timing) MCFD_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
+  ctx->launches++;
+  return MCFD_OK;
+}
+
+template <bool kToTiles>
+int LaunchConvert(mcfd_ctx *ctx, double *tiles, double *column, const int *cells, int64_t n_items) {
+  if (n_items == 0) return MCFD_OK;
+  int blocks = (int)((n_items + kTile - 1) / kTile);
+  cudaError_t e;
+  if (ctx->q == 3) {
+    constexpr int F = 135;
+    size_t smem = (size_t)kTile * (F + 1) * sizeof(double);
+    ConvertKernel<F, kToTiles><<<blocks, 256, smem, ctx->stream>>>(tiles, column, cells, (int)n_items);
+    e = cudaGetLastError();
+  } else {
+    constexpr int F = 320;
+    size_t smem = (size_t)kTile * (F + 1) * sizeof(double);
+    auto kernel = ConvertKernel<F, kToTiles>;
+    static bool configured = false;
+    if (!configured) {
+      e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return Fail(ctx, MCFD_ERR_CUDA, cudaGetErrorString(e));
+      configured = true;
+    }
+    kernel<<<blocks, 256, smem, ctx->stream>>>(tiles, column, cells, (int)n_items);
+    e = cudaGetLastError();
+  }
+  if (e != cudaSuccess) return Fail(ctx, MCFD_ERR_CUDA, std::string("convert kernel: ") + cudaGetErrorString(e));
+  ctx->launches++;
+  return MCFD_OK;
+}
+
+int RequireMesh(mcfd_ctx *ctx) {
+  if (!ctx) return MCFD_ERR_ARG;
+  if (!ctx->has_mesh) return Fail(ctx, MCFD_ERR_STATE, "mcfd_set_mesh has not been called");
+  return MCFD_OK;
+}
+
+int EnsureColumn(mcfd_ctx *ctx) {
+  size_t need = (size_t)ctx->mesh.n_local * ctx->fields;
+  if (ctx->column.n < need) MCFD_CUDA(ctx, ctx->column.Alloc(need));
+  return MCFD_OK;
+}
+
+// row-per-cell host array -> tile layout
+template <class T>
+std::vector<T> ToTiles(const std::vector<T> &src, int rows, int64_t n_cells, int64_t n_tiles) {
+  std::vector<T> out((size_t)n_tiles * rows * kTile, T{});
+  for (int64_t c = 0; c < n_cells; ++c)
+    for (int r = 0; r < rows; ++r)
+      out[((c >> 5) * rows + r) * kTile + (c & 31)] = src[c * rows + r];
+  return out;
+}
+
+void StageBuffers(mcfd_ctx *ctx, int stage, int *in, int *out, int *mode) {
+  // three buffers rotate: u0 stays put for the whole step
+  const int u0 = ctx->rk_u0, a = (u0 + 1) % 3, b = (u0 + 2) % 3;
+  if (ctx->rk_order == 1) { *in = u0; *out = a; *mode = kModeEuler; return; }
+  if (ctx->rk_order == 2) {
+    if (stage == 0) { *in = u0; *out = a; *mode = kModeEuler; }
+    else { *in = a; *out = b; *mode = kModeRk2b; }
+    return;
+  }
+  if (stage == 0) { *in = u0; *out = a; *mode = kModeEuler; }
+  else if (stage == 1) { *in = a; *out = b; *mode = kModeRk3b; }
+  else { *in = b; *out = a; *mode = kModeRk3c; }
+}
+
+}  // namespace
+
+extern "C" {
+
+int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
+  if (!config || !ctx_out) return Fail(nullptr, MCFD_ERR_ARG, "null argument");
+  if (config->degree != 2 && config->degree != 3)
+    return Fail(nullptr, MCFD_ERR_ARG, "degree must be 2 or 3");
+  if (config->scheme != MCFD_FR_LOBATTO && config->scheme != MCFD_DG_LOBATTO)
+    return Fail(nullptr, MCFD_ERR_ARG, "unknown scheme");
+  if (config->riemann < MCFD_EXACT || config->riemann > MCFD_AUSM)
+    return Fail(nullptr, MCFD_ERR_ARG, "unknown Riemann solver");
+  int n_dev = 0;
+  cudaError_t e = cudaGetDeviceCount(&n_dev);
+  if (e != cudaSuccess || n_dev == 0)
+    return Fail(nullptr, MCFD_ERR_CUDA, std::string("no CUDA device: ") +
+        (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0") +
+        " (libminicfd_b200 has no CPU fallback)");
+  if (config->device >= 0) {
+    e = cudaSetDevice(config->device);
+    if (e != cudaSuccess) return Fail(nullptr, MCFD_ERR_CUDA, cudaGetErrorString(e));
+  }
+  auto ctx = std::make_unique<mcfd_ctx>();
+  ctx->cfg = *config;
+  ctx->q = config->degree + 1;
+  ctx->n_nodes = ctx->q * ctx->q * ctx->q;
+  ctx->fields = 5 * ctx->n_nodes;
+  ctx->cpb = (ctx->q == 3) ? 32 : 16;
+  ctx->n_warps = (ctx->q == 3) ? 9 : 16;
+  ctx->tables = BuildTables(config->degree, config->scheme, ctx->n_warps, kTile / ctx->cpb);
+  e = cudaMemcpyToSymbol(c_tab, &ctx->tables, sizeof(Tables));
+  if (e != cudaSuccess) return Fail(nullptr, MCFD_ERR_CUDA, cudaGetErrorString(e));
+  e = ctx->dt_bits.Alloc(1);
+  if (e != cudaSuccess) return Fail(nullptr, MCFD_ERR_CUDA, cudaGetErrorString(e));
+  *ctx_out = ctx.release();
+  return MCFD_OK;
+}
+
+int mcfd_destroy(mcfd_ctx *ctx) {
+  if (!ctx) return MCFD_OK;
+  for (auto &p : ctx->events) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
+  delete ctx;
+  return MCFD_OK;
+}
+
+const char *mcfd_last_error(const mcfd_ctx *ctx) {
+  return ctx ? ctx->error.c_str() : g_create_error.c_str();
+}
+
+int mcfd_set_stream(mcfd_ctx *ctx, void *cuda_stream) {
+  if (!ctx) return MCFD_ERR_ARG;
+  ctx->stream = static_cast<cudaStream_t>(cuda_stream);
+  return MCFD_OK;
+}
+
+int mcfd_set_mesh(mcfd_ctx *ctx, int64_t n_nodes, const double *xyz, int64_t n_local,
+    int64_t n_ghost, const int64_t *cell_nodes, int64_t n_bfaces, const int64_t *bface_nodes,
+    const int32_t *bface_tags, int64_t n_pairs, const int64_t *periodic_pairs) {
+  if (!ctx || !xyz || !cell_nodes || n_local <= 0 || n_ghost < 0)
+    return Fail(ctx, MCFD_ERR_ARG, "bad mesh arguments");
+  if (n_local + n_ghost > (int64_t)1 << 30) return Fail(ctx, MCFD_ERR_ARG, "too many cells for int32 ids");
+  // the tables are per context but live in one __constant__ symbol: refresh
+  MCFD_CUDA(ctx, cudaMemcpyToSymbol(c_tab, &ctx->tables, sizeof(Tables)));
+  ctx->mesh = HostMesh();
+  if (!ctx->mesh.Build(ctx->cfg.degree, n_nodes, xyz, n_local, n_ghost, cell_nodes, n_bfaces,
+          bface_nodes, bface_tags, n_pairs, periodic_pairs))
+    return Fail(ctx, MCFD_ERR_MESH, ctx->mesh.error);
+  ctx->n_cells = n_local + n_ghost;
+  ctx->n_tiles = (ctx->n_cells + kTile - 1) / kTile;
+  auto geom = ToTiles(ctx->mesh.coef, kGeomRows, ctx->n_cells, ctx->n_tiles);
+  auto nbr = ToTiles(ctx->mesh.nbr, 6, ctx->n_cells, ctx->n_tiles);
+  auto code = ToTiles(ctx->mesh.code, 6, ctx->n_cells, ctx->n_tiles);
+  MCFD_CUDA(ctx, ctx->geom.Alloc(geom.size()));
+  MCFD_CUDA(ctx, ctx->nbr.Alloc(nbr.size()));
+  MCFD_CUDA(ctx, ctx->code.Alloc(code.size()));
+  MCFD_CUDA(ctx, cudaMemcpy(ctx->geom.p, geom.data(), geom.size() * sizeof(double), cudaMemcpyHostToDevice));
+  MCFD_CUDA(ctx, cudaMemcpy(ctx->nbr.p, nbr.data(), nbr.size() * sizeof(int), cudaMemcpyHostToDevice));
+  MCFD_CUDA(ctx, cudaMemcpy(ctx->code.p, code.data(), code.size(), cudaMemcpyHostToDevice));
+  MCFD_CUDA(ctx, ctx->length.Alloc(n_local));
+  MCFD_CUDA(ctx, cudaMemcpy(ctx->length.p, ctx->mesh.length.data(), n_local * sizeof(double), cudaMemcpyHostToDevice));
+  size_t state = (size_t)ctx->n_tiles * ctx->fields * kTile;
+  for (auto &b : ctx->u) {
+    MCFD_CUDA(ctx, b.Alloc(state));
+    MCFD_CUDA(ctx, cudaMemset(b.p, 0, state * sizeof(double)));
+  }
+  ctx->res.Free();
+  size_t nb = ctx->mesh.bound_faces.size();
+  ctx->btag_of_face.resize(nb);
+  for (size_t b = 0; b < nb; ++b) ctx->btag_of_face[b] = ctx->mesh.bound_faces[b].tag;
+  ctx->bkind_host.assign(nb, MCFD_BC_INVISCID_WALL);
+  for (size_t b = 0; b < nb; ++b) {
+    auto it = ctx->tag_kind.find(ctx->btag_of_face[b]);
+    if (it != ctx->tag_kind.end()) ctx->bkind_host[b] = (unsigned char)it->second;
+  }
+  MCFD_CUDA(ctx, ctx->bkind.Alloc(std::max<size_t>(nb, 1)));
+  MCFD_CUDA(ctx, ctx->bvals.Alloc(std::max<size_t>(nb, 1) * ctx->q * ctx->q * 5));
+  MCFD_CUDA(ctx, cudaMemset(ctx->bvals.p, 0, ctx->bvals.n * sizeof(double)));
+  if (nb) MCFD_CUDA(ctx, cudaMemcpy(ctx->bkind.p, ctx->bkind_host.data(), nb, cudaMemcpyHostToDevice));
+  // CTA blocks that contain only inner cells: cells are ordered inner first (part.hpp:746-767);
+  // a local cell is "inter" when one of its neighbours is a ghost.
+  int64_t first_inter = n_local;
+  for (int64_t c = 0; c < n_local && first_inter == n_local; ++c)
+    for (int f = 0; f < 6; ++f)
+      if (ctx->mesh.nbr[c * 6 + f] >= n_local) { first_inter = c; break; }
+  ctx->total_blocks = (n_local + ctx->cpb - 1) / ctx->cpb;
+  ctx->inner_blocks = first_inter / ctx->cpb;
+  ctx->send_cells.Free(); ctx->recv_cells.Free(); ctx->send_buf.Free(); ctx->recv_buf.Free();
+  ctx->cur = 0;
+  ctx->has_mesh = true;
+  return MCFD_OK;
+}
+
+int64_t mcfd_get_faces(const mcfd_ctx *ctx, int kind, int64_t *holder, int64_t *sharer,
+    int32_t *holder_face, int32_t *sharer_face, int32_t *orientation) {
+  if (!ctx || !ctx->has_mesh) return MCFD_ERR_STATE;
+  auto const &faces = kind == 0 ? ctx->mesh.local_faces : kind == 1 ? ctx->mesh.ghost_faces
+                                                                    : ctx->mesh.bound_faces;
+  for (size_t i = 0; i < faces.size(); ++i) {
+    if (holder) holder[i] = faces[i].holder;
+    if (sharer) sharer[i] = faces[i].sharer;
+    if (holder_face) holder_face[i] = faces[i].holder_face;
+    if (sharer_face) sharer_face[i] = faces[i].sharer_face;
+    if (orientation) orientation[i] = faces[i].orientation;
+  }
+  return (int64_t)faces.size();
+}
+
+int mcfd_get_cell_geometry(const mcfd_ctx *ctx, double *length, double *volume) {
+  if (!ctx || !ctx->has_mesh) return MCFD_ERR_STATE;
+  if (length) std::memcpy(length, ctx->mesh.length.data(), ctx->mesh.length.size() * sizeof(double));
+  if (volume) std::memcpy(volume, ctx->mesh.volume.data(), ctx->mesh.volume.size() * sizeof(double));
+  return MCFD_OK;
+}
+
+int mcfd_set_halo(mcfd_ctx *ctx, int32_t n_send_parts, const int64_t *send_counts,
+    const int64_t *send_cells, int32_t n_recv_parts, const int64_t *recv_counts,
+    const int64_t *recv_cells) {
+  if (int s = RequireMesh(ctx)) return s;
+  int64_t ns = 0, nr = 0;
+  for (int i = 0; i < n_send_parts; ++i) ns += send_counts[i];
+  for (int i = 0; i < n_recv_parts; ++i) nr += recv_counts[i];
+  std::vector<int> s32(ns), r32(nr);
+  for (int64_t i = 0; i < ns; ++i) {
+    if (send_cells[i] < 0 || send_cells[i] >= ctx->mesh.n_local)
+      return Fail(ctx, MCFD_ERR_ARG, "send cell is not a local cell");
+    s32[i] = (int)send_cells[i];
+  }
+  for (int64_t i = 0; i < nr; ++i) {
+    if (recv_cells[i] < ctx->mesh.n_local || recv_cells[i] >= ctx->n_cells)
+      return Fail(ctx, MCFD_ERR_ARG, "recv cell is not a ghost cell");
+    r32[i] = (int)recv_cells[i];
+  }
+  MCFD_CUDA(ctx, ctx->send_cells.Alloc(ns));
+  MCFD_CUDA(ctx, ctx->recv_cells.Alloc(nr));
+  MCFD_CUDA(ctx, ctx->send_buf.Alloc(ns * ctx->fields));
+  MCFD_CUDA(ctx, ctx->recv_buf.Alloc(nr * ctx->fields));
+  if (ns) MCFD_CUDA(ctx, cudaMemcpy(ctx->send_cells.p, s32.data(), ns * sizeof(int), cudaMemcpyHostToDevice));
+  if (nr) MCFD_CUDA(ctx, cudaMemcpy(ctx->recv_cells.p, r32.data(), nr * sizeof(int), cudaMemcpyHostToDevice));
+  return MCFD_OK;
+}
+
+int mcfd_halo_buffers(mcfd_ctx *ctx, double **send_dev, int64_t *send_doubles, double **recv_dev,
+    int64_t *recv_doubles) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (send_dev) *send_dev = ctx->send_buf.p;
+  if (send_doubles) *send_doubles = (int64_t)ctx->send_buf.n;
+  if (recv_dev) *recv_dev = ctx->recv_buf.p;
+  if (recv_doubles) *recv_doubles = (int64_t)ctx->recv_buf.n;
+  return MCFD_OK;
+}
+
+// The buffer that the next residual / stage reads: the current solution outside a step, the stage
+// input inside one.
+static double *HaloState(mcfd_ctx *ctx) { return ctx->u[ctx->rk_order ? ctx->rk_in : ctx->cur].p; }
+
+int mcfd_halo_pack(mcfd_ctx *ctx) {
+  if (int s = RequireMesh(ctx)) return s;
+  return LaunchConvert<false>(ctx, HaloState(ctx), ctx->send_buf.p, ctx->send_cells.p,
+      (int64_t)ctx->send_cells.n);
+}
+
+int mcfd_halo_unpack(mcfd_ctx *ctx) {
+  if (int s = RequireMesh(ctx)) return s;
+  return LaunchConvert<true>(ctx, HaloState(ctx), ctx->recv_buf.p, ctx->recv_cells.p,
+      (int64_t)ctx->recv_cells.n);
+}
+
+int mcfd_set_boundary(mcfd_ctx *ctx, int32_t tag, int32_t bc_kind) {
+  if (!ctx) return MCFD_ERR_ARG;
+  if (bc_kind < MCFD_BC_INVISCID_WALL || bc_kind > MCFD_BC_NO_SLIP_WALL)
+    return Fail(ctx, MCFD_ERR_ARG, "unknown boundary kind");
+  ctx->tag_kind[tag] = bc_kind;
+  if (ctx->has_mesh) {
+    size_t nb = ctx->bkind_host.size();
+    for (size_t b = 0; b < nb; ++b)
+      if (ctx->btag_of_face[b] == tag) ctx->bkind_host[b] = (unsigned char)bc_kind;
+    if (nb) MCFD_CUDA(ctx, cudaMemcpyAsync(ctx->bkind.p, ctx->bkind_host.data(), nb, cudaMemcpyHostToDevice, ctx->stream));
+    MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  }
+  return MCFD_OK;
+}
+
+int64_t mcfd_count_boundary_faces(const mcfd_ctx *ctx, int32_t tag) {
+  if (!ctx || !ctx->has_mesh) return MCFD_ERR_STATE;
+  int64_t n = 0;
+  for (int32_t t : ctx->btag_of_face) n += (t == tag);
+  return n;
+}
+
+int mcfd_get_boundary_points(const mcfd_ctx *ctx, int32_t tag, double *xyz) {
+  if (!ctx || !ctx->has_mesh || !xyz) return MCFD_ERR_STATE;
+  ctx->mesh.BoundaryPoints(ctx->tables, ctx->cfg.degree, tag, xyz);
+  return MCFD_OK;
+}
+
+int mcfd_set_boundary_values(mcfd_ctx *ctx, int32_t tag, const double *values) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (!values) return Fail(ctx, MCFD_ERR_ARG, "null values");
+  const size_t per_face = (size_t)ctx->q * ctx->q * 5;
+  // faces of one tag are contiguous in the boundary table (grouped by tag)
+  size_t nb = ctx->btag_of_face.size(), first = nb, count = 0;
+  for (size_t b = 0; b < nb; ++b)
+    if (ctx->btag_of_face[b] == tag) { if (first == nb) first = b; ++count; }
+  if (count == 0) return MCFD_OK;
+  MCFD_CUDA(ctx, cudaMemcpyAsync(ctx->bvals.p + first * per_face, values,
+      count * per_face * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // `values` may be reused by the caller
+  return MCFD_OK;
+}
+
+int mcfd_set_time_callback(mcfd_ctx *ctx, mcfd_time_callback fn, void *user) {
+  if (!ctx) return MCFD_ERR_ARG;
+  ctx->time_cb = fn;
+  ctx->time_user = user;
+  return MCFD_OK;
+}
+
+int64_t mcfd_count_local_cells(const mcfd_ctx *ctx) {
+  return (ctx && ctx->has_mesh) ? ctx->mesh.n_local : (int64_t)MCFD_ERR_STATE;
+}
+
+int64_t mcfd_cell_data_size(const mcfd_ctx *ctx) {
+  return (ctx && ctx->has_mesh) ? ctx->mesh.n_local * ctx->fields : (int64_t)MCFD_ERR_STATE;
+}
+
+int mcfd_set_solution_device(mcfd_ctx *ctx, const double *column_dev) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (ctx->rk_order) return Fail(ctx, MCFD_ERR_STATE, "an RK step is open");
+  return LaunchConvert<true>(ctx, ctx->u[ctx->cur].p, const_cast<double *>(column_dev), nullptr,
+      ctx->mesh.n_local);
+}
+
+int mcfd_get_solution_device(mcfd_ctx *ctx, double *column_dev) {
+  if (int s = RequireMesh(ctx)) return s;
+  return LaunchConvert<false>(ctx, ctx->u[ctx->cur].p, column_dev, nullptr, ctx->mesh.n_local);
+}
+
+int mcfd_set_solution(mcfd_ctx *ctx, const double *column) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (!column) return Fail(ctx, MCFD_ERR_ARG, "null column");
+  if (int s = EnsureColumn(ctx)) return s;
+  size_t bytes = (size_t)ctx->mesh.n_local * ctx->fields * sizeof(double);
+  MCFD_CUDA(ctx, cudaMemcpyAsync(ctx->column.p, column, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  if (int s = mcfd_set_solution_device(ctx, ctx->column.p)) return s;
+  MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return MCFD_OK;
+}
+
+int mcfd_get_solution(mcfd_ctx *ctx, double *column) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (!column) return Fail(ctx, MCFD_ERR_ARG, "null column");
+  if (int s = EnsureColumn(ctx)) return s;
+  if (int s = mcfd_get_solution_device(ctx, ctx->column.p)) return s;
+  size_t bytes = (size_t)ctx->mesh.n_local * ctx->fields * sizeof(double);
+  MCFD_CUDA(ctx, cudaMemcpyAsync(column, ctx->column.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return MCFD_OK;
+}
+
+int mcfd_residual(mcfd_ctx *ctx, double t, double *column, double *column_dev) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (ctx->rk_order) return Fail(ctx, MCFD_ERR_STATE, "an RK step is open");
+  size_t state = (size_t)ctx->n_tiles * ctx->fields * kTile;
+  if (ctx->res.n < state) MCFD_CUDA(ctx, ctx->res.Alloc(state));
+  if (ctx->time_cb) ctx->time_cb(ctx->time_user, t);
+  const double *u = ctx->u[ctx->cur].p;
+  if (int s = LaunchStage(ctx, u, u, ctx->res.p, kModeResidual, 0.0, 0, ctx->total_blocks)) return s;
+  if (column_dev) {
+    if (int s = LaunchConvert<false>(ctx, ctx->res.p, column_dev, nullptr, ctx->mesh.n_local)) return s;
+  }
+  if (column) {
+    if (int s = EnsureColumn(ctx)) return s;
+    if (int s = LaunchConvert<false>(ctx, ctx->res.p, ctx->column.p, nullptr, ctx->mesh.n_local)) return s;
+    size_t bytes = (size_t)ctx->mesh.n_local * ctx->fields * sizeof(double);
+    MCFD_CUDA(ctx, cudaMemcpyAsync(column, ctx->column.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return MCFD_OK;
+}
+
+int mcfd_rk_begin(mcfd_ctx *ctx, int order, double t, double dt) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (order < 1 || order > 3) return Fail(ctx, MCFD_ERR_ARG, "RK order must be 1, 2 or 3");
+  if (ctx->rk_order) return Fail(ctx, MCFD_ERR_STATE, "an RK step is already open");
+  ctx->rk_order = order;
+  ctx->rk_u0 = ctx->cur;
+  ctx->rk_in = ctx->cur;
+  ctx->rk_t = t;
+  ctx->rk_dt = dt;
+  return MCFD_OK;
+}
+
+double mcfd_rk_stage_time(const mcfd_ctx *ctx, int stage) {
+  // rk.hpp:16-49: RK1 (t); RK2 (t, t+dt); RK3 (t, t+dt, t+dt/2)
+  if (stage == 0) return ctx->rk_t;
+  if (stage == 1) return ctx->rk_t + ctx->rk_dt;
+  return ctx->rk_t + ctx->rk_dt / 2;
+}
+
+int mcfd_rk_stage_inner(mcfd_ctx *ctx, int stage) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (!ctx->rk_order || stage < 0 || stage >= ctx->rk_order)
+    return Fail(ctx, MCFD_ERR_STATE, "no such stage in the open RK step");
+  int in, out, mode;
+  StageBuffers(ctx, stage, &in, &out, &mode);
+  if (in != ctx->rk_in) return Fail(ctx, MCFD_ERR_STATE, "stages must be run in order");
+  if (ctx->time_cb) ctx->time_cb(ctx->time_user, mcfd_rk_stage_time(ctx, stage));
+  return LaunchStage(ctx, ctx->u[in].p, ctx->u[ctx->rk_u0].p, ctx->u[out].p, mode, ctx->rk_dt, 0,
+      ctx->inner_blocks);
+}
+
+int mcfd_rk_stage_inter(mcfd_ctx *ctx, int stage) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (!ctx->rk_order || stage < 0 || stage >= ctx->rk_order)
+    return Fail(ctx, MCFD_ERR_STATE, "no such stage in the open RK step");
+  int in, out, mode;
+  StageBuffers(ctx, stage, &in, &out, &mode);
+  if (in != ctx->rk_in) return Fail(ctx, MCFD_ERR_STATE, "stages must be run in order");
+  if (int s = LaunchStage(ctx, ctx->u[in].p, ctx->u[ctx->rk_u0].p, ctx->u[out].p, mode, ctx->rk_dt,
+          ctx->inner_blocks, ctx->total_blocks)) return s;
+  ctx->rk_in = out;
+  if (stage == ctx->rk_order - 1) {  // step complete
+    ctx->cur = out;
+    ctx->rk_order = 0;
+  }
+  return MCFD_OK;
+}
+
+int mcfd_rk_step(mcfd_ctx *ctx, int order, double t, double dt) {
+  if (int s = mcfd_rk_begin(ctx, order, t, dt)) return s;
+  for (int stage = 0; stage < order; ++stage) {
+    if (int s = mcfd_rk_stage_inner(ctx, stage)) { ctx->rk_order = 0; return s; }
+    if (int s = mcfd_rk_stage_inter(ctx, stage)) { ctx->rk_order = 0; return s; }
+  }
+  return MCFD_OK;
+}
+
+int mcfd_time_step(mcfd_ctx *ctx, double dt_guess, int rk_order, double *dt_local) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (!dt_local || rk_order < 0 || rk_order > 4) return Fail(ctx, MCFD_ERR_ARG, "bad arguments");
+  // fem.hpp:26-37
+  static const double cfl[5][9] = {
+    {1.000},
+    {1.000, 0.333},
+    {1.000, 0.333, 0.209, 0.130, 0.089, 0.066, 0.051, 0.040, 0.033},
+    {1.256, 0.409, 0.209, 0.130, 0.089, 0.066, 0.051, 0.040, 0.033},
+    {1.392, 0.464, 0.235, 0.145, 0.100, 0.073, 0.056, 0.045, 0.037}};
+  double big = 1e100;
+  unsigned long long bits;
+  std::memcpy(&bits, &big, sizeof(bits));
+  MCFD_CUDA(ctx, cudaMemcpyAsync(ctx->dt_bits.p, &bits, sizeof(bits), cudaMemcpyHostToDevice, ctx->stream));
+  int n = (int)ctx->mesh.n_local, threads = 128, blocks = (n + threads - 1) / threads;
+  if (ctx->q == 3) TimeStepKernel<3><<<blocks, threads, 0, ctx->stream>>>(ctx->u[ctx->cur].p, ctx->length.p, n, ctx->dt_bits.p);
+  else TimeStepKernel<4><<<blocks, threads, 0, ctx->stream>>>(ctx->u[ctx->cur].p, ctx->length.p, n, ctx->dt_bits.p);
+  MCFD_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  MCFD_CUDA(ctx, cudaMemcpyAsync(&bits, ctx->dt_bits.p, sizeof(bits), cudaMemcpyDeviceToHost, ctx->stream));
+  MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  double min_dt;
+  std::memcpy(&min_dt, &bits, sizeof(bits));
+  double dt = std::min(cfl[rk_order][ctx->cfg.degree] * min_dt, dt_guess);  // fem.hpp:433-434
+  if (ctx->cfg.scheme == MCFD_FR_LOBATTO) dt = std::min(dt_guess, 2.0 * dt);  // fr/lobatto.hpp:220-222
+  *dt_local = dt;
+  return MCFD_OK;
+}
+
+int64_t mcfd_launch_count(const mcfd_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int mcfd_enable_kernel_timing(mcfd_ctx *ctx, int enable) {
+  if (!ctx) return MCFD_ERR_ARG;
+  ctx->timing = enable != 0;
+  ctx->events_used = 0;
+  return MCFD_OK;
+}
+
+int mcfd_kernel_time(mcfd_ctx *ctx, double *total_ms, int64_t *n_launches, int reset) {
+  if (!ctx) return MCFD_ERR_ARG;
+  MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  double total = 0;
+  for (size_t i = 0; i < ctx->events_used; ++i) {
+    float ms = 0;
+    MCFD_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->events[i].first, ctx->events[i].second));
+    total += ms;
+  }
+  if (total_ms) *total_ms = total;
+  if (n_launches) *n_launches = (int64_t)ctx->events_used;
+  if (reset) ctx->events_used = 0;
+  return MCFD_OK;
+}
+
+int mcfd_riemann_flux(mcfd_ctx *ctx, int32_t bc_kind, int64_t n, const double *normals,
+    const double *u_left, const double *u_right, double *flux) {
+  if (!ctx || n <= 0) return MCFD_ERR_ARG;
+  DevBuf<double> dn, dl, dr, df;
+  MCFD_CUDA(ctx, dn.Alloc(3 * n));
+  MCFD_CUDA(ctx, dl.Alloc(5 * n));
+  MCFD_CUDA(ctx, dr.Alloc(5 * n));
+  MCFD_CUDA(ctx, df.Alloc(5 * n));
+  MCFD_CUDA(ctx, cudaMemcpy(dn.p, normals, 3 * n * sizeof(double), cudaMemcpyHostToDevice));
+  MCFD_CUDA(ctx, cudaMemcpy(dl.p, u_left, 5 * n * sizeof(double), cudaMemcpyHostToDevice));
+  MCFD_CUDA(ctx, cudaMemcpy(dr.p, u_right, 5 * n * sizeof(double), cudaMemcpyHostToDevice));
+  int threads = 128, blocks = (int)((n + threads - 1) / threads);
+  switch (ctx->cfg.riemann) {
+  case MCFD_EXACT: RiemannKernel<kExact><<<blocks, threads, 0, ctx->stream>>>(bc_kind, (int)n, dn.p, dl.p, dr.p, df.p); break;
+  case MCFD_HLLC: RiemannKernel<kHllc><<<blocks, threads, 0, ctx->stream>>>(bc_kind, (int)n, dn.p, dl.p, dr.p, df.p); break;
+  default: RiemannKernel<kAusm><<<blocks, threads, 0, ctx->stream>>>(bc_kind, (int)n, dn.p, dl.p, dr.p, df.p); break;
+  }
+  MCFD_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  MCFD_CUDA(ctx, cudaMemcpy(flux, df.p, 5 * n * sizeof(double), cudaMemcpyDeviceToHost));
+  return MCFD_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,425 @@
+// physics.cuh — ideal-gas Euler fluxes, Riemann solvers and boundary fluxes, device side.
+//
+// Restates the arithmetic of the reference's include/mini/riemann/euler/{types,exact,hllc,ausm}.hpp
+// and include/mini/riemann/rotated/euler.hpp for one flux point.  Written tangent-free: the
+// reference rotates the momentum into the face frame (normal, tangent, bitangent) and back
+// (rotated/euler.hpp:117-134); all three solvers treat the tangential velocity as passively
+// advected, so the tangential momentum flux is a scalar times the tangential velocity *vector* of
+// one side (or, for AUSM, of each side).  We therefore carry  v_t = v - (v.n) n  as a 3-vector and
+// never need the tangents.  Identical in exact arithmetic, differs by rounding only.
+#ifndef MINICFD_B200_PHYSICS_CUH_
+#define MINICFD_B200_PHYSICS_CUH_
+
+#ifdef __CUDACC__
+#include <cuda_runtime.h>
+#define MCFD_HD __device__ __forceinline__
+#define MCFD_CONSTANT __constant__
+#else  // host build of the same source: tests/host_emulation only
+#include <cmath>
+#define MCFD_HD inline
+#define MCFD_CONSTANT static
+using std::fma; using std::fmax; using std::fmin; using std::pow; using std::sqrt;
+#endif
+
+namespace mcfd {
+
+// IdealGas<double, 1.4> constants (types.hpp:206-247)
+constexpr double kGamma = 1.4;
+constexpr double kGasR = 287.05;
+constexpr double kGm1 = kGamma - 1;                       // GammaMinusOne
+constexpr double kOneOverGm1 = 1 / kGm1;                  // OneOverGammaMinusOne
+constexpr double kGp1Over2 = (kGamma + 1) / 2;            // GammaPlusOneOverTwo
+constexpr double kGp1Over4 = (kGamma + 1) / 4;            // GammaPlusOneOverFour
+constexpr double kGm1Over2 = kGm1 / 2;                    // GammaMinusOneOverTwo
+constexpr double kGm1Under2 = 2 / kGm1;                   // GammaMinusOneUnderTwo
+constexpr double kOneOverGamma = 1 / kGamma;
+constexpr double kGammaOverGm1 = kGamma / kGm1;
+
+enum : int { kExact = 0, kHllc = 1, kAusm = 2 };
+
+struct Prim {
+  double rho, u, v, w, p;  // velocity in the global frame
+};
+
+// IdealGas::ConservativeToPrimitive incl. SetZeroIfNegative (types.hpp:194-202, 289-301).
+MCFD_HD Prim ConsToPrim(double r, double mx, double my, double mz, double e) {
+  Prim q;
+  if (r < 0 || e < 0) {  // the energy slot is tested before it becomes a pressure
+    q.rho = q.u = q.v = q.w = q.p = 0;
+    return q;
+  }
+  if (r != 0) {
+    double inv = 1.0 / r;
+    q.rho = r;
+    q.u = mx * inv;
+    q.v = my * inv;
+    q.w = mz * inv;
+    double ke = 0.5 * (q.u * q.u + q.v * q.v + q.w * q.w);
+    q.p = (e - r * ke) * kGm1;
+    if (q.p < 0) {
+      q.rho = q.u = q.v = q.w = q.p = 0;
+    }
+  } else {  // rho == 0: returned unchanged by the reference
+    q.rho = 0; q.u = mx; q.v = my; q.w = mz; q.p = e;
+  }
+  return q;
+}
+
+// IdealGas::GetSpeedOfSound (types.hpp:252-254)
+MCFD_HD double SoundSpeed(double rho, double p) {
+  return (rho > 0 && p > 0) ? sqrt(kGamma * p / rho) : 0.0;
+}
+
+// Result of a 1-D solver in the normal frame: mass, normal momentum and energy flux plus the
+// factors multiplying the left / right tangential velocity vectors.
+struct NormalFlux {
+  double mass, mom_n, energy, c_left, c_right;
+};
+
+// Gas::PrimitiveToFlux (types.hpp:313-320) for a state with normal velocity un and kinetic energy ke.
+MCFD_HD void StateFlux(double rho, double un, double p, double ke,
+    double *mass, double *mom_n, double *energy) {
+  double e = p * kOneOverGm1 + rho * ke;
+  double m = rho * un;
+  *mass = m;
+  *mom_n = m * un + p;
+  *energy = e * un + p * un;
+}
+
+// ---- HLLC (hllc.hpp:30-44, 54-109) -------------------------------------------------------------
+MCFD_HD double HllcQ(double p_est, double p_k) {
+  if (p_est <= p_k) return 1.0;
+  return sqrt(1 + kGp1Over2 * (p_est / p_k - 1) / kGamma);
+}
+
+MCFD_HD NormalFlux HllcStar(double rho, double un, double p, double ke,
+    double wave_k, double wave_star) {
+  NormalFlux f;
+  StateFlux(rho, un, p, ke, &f.mass, &f.mom_n, &f.energy);
+  double energy = p * kOneOverGm1 + rho * ke;
+  double temp = rho * (wave_k - un) / (wave_k - wave_star);
+  double e_star = energy / rho + (wave_star - un) * (wave_star + p / (rho * (wave_k - un)));
+  e_star *= temp;
+  f.mass += (temp - rho) * wave_k;
+  f.mom_n += (temp * wave_star - rho * un) * wave_k;
+  f.energy += (e_star - energy) * wave_k;
+  f.c_left = f.c_right = 0;
+  return f;
+}
+
+MCFD_HD NormalFlux SolveHllc(double rl, double ul, double pl, double kel,
+    double rr, double ur, double pr, double ker) {
+  double rho_avg = (rl + rr) / 2;
+  double al = SoundSpeed(rl, pl), ar = SoundSpeed(rr, pr);
+  double a_avg = (al + ar) / 2;
+  double p_pvrs = (pl + pr - (ur - ul) * rho_avg * a_avg) / 2;
+  double p_est = fmax(0.0, p_pvrs);
+  double wl = ul - al * HllcQ(p_est, pl);
+  double wr = ur + ar * HllcQ(p_est, pr);
+  double ws = (pr - pl + rl * ul * (wl - ul) - rr * ur * (wr - ur)) /
+              (rl * (wl - ul) - rr * (wr - ur));
+  NormalFlux f;
+  f.c_left = f.c_right = 0;
+  if (0.0 <= wl) {
+    StateFlux(rl, ul, pl, kel, &f.mass, &f.mom_n, &f.energy);
+    f.c_left = f.mass;
+  } else if (wr <= 0.0) {
+    StateFlux(rr, ur, pr, ker, &f.mass, &f.mom_n, &f.energy);
+    f.c_right = f.mass;
+  } else if (0.0 <= ws) {
+    f = HllcStar(rl, ul, pl, kel, wl, ws);
+    f.c_left = f.mass;
+  } else {
+    f = HllcStar(rr, ur, pr, ker, wr, ws);
+    f.c_right = f.mass;
+  }
+  return f;
+}
+
+// ---- AUSM (ausm.hpp:30-33, 52-71) --------------------------------------------------------------
+template <bool kNegative>
+MCFD_HD void AusmSigned(double rho, double un, double p_in, double ke,
+    double *m_out, double *p_out, double *h_out) {
+  double a = SoundSpeed(rho, p_in);
+  double h = a * a / kGm1 + ke;
+  double mach = un / a;
+  double p = p_in;
+  double signed_mach = (1 + (kNegative ? -mach : mach)) * 0.5;
+  if (mach >= -1 && mach <= 1) {
+    mach = kNegative ? -(signed_mach * signed_mach) : signed_mach * signed_mach;
+    p *= signed_mach;
+  } else if (signed_mach < 0) {
+    mach = 0.0;
+    p = 0.0;
+  }
+  *m_out = rho * a * mach;
+  *p_out = p;
+  *h_out = h;
+}
+
+MCFD_HD NormalFlux SolveAusm(double rl, double ul, double pl, double kel,
+    double rr, double ur, double pr, double ker) {
+  double ml, ppl, hl, mr, ppr, hr;
+  AusmSigned<false>(rl, ul, pl, kel, &ml, &ppl, &hl);
+  AusmSigned<true>(rr, ur, pr, ker, &mr, &ppr, &hr);
+  NormalFlux f;
+  f.mass = ml + mr;
+  f.mom_n = (ml * ul + ppl) + (mr * ur + ppr);
+  f.energy = ml * hl + mr * hr;
+  f.c_left = ml;
+  f.c_right = mr;
+  return f;
+}
+
+// ---- Exact (exact.hpp:36-46, 62-320) -----------------------------------------------------------
+struct SpeedChange {  // exact.hpp:153-200
+  double rho_b, p_b, a_b, p_const;
+  MCFD_HD SpeedChange(double rho, double p)
+      : rho_b(rho), p_b(p), a_b(rho == 0 ? 0 : SoundSpeed(rho, p)), p_const(p * kGm1Over2) {}
+  MCFD_HD double P(double pa) const { return kGp1Over2 * pa + p_const; }
+  MCFD_HD double Value(double pa) const {
+    if (pa >= p_b) {
+      return (pa - p_b) / sqrt(rho_b * P(pa));
+    }
+    constexpr double e = kGm1Over2 / kGamma;
+    return (pow(pa / p_b, e) - 1) * (kGm1Under2 * a_b);
+  }
+  MCFD_HD double Prime(double pa) const {
+    if (pa >= p_b) {
+      double pp = P(pa);
+      double v = kGp1Over4 * (p_b - pa);
+      return (1 + v / pp) / sqrt(rho_b * pp);
+    }
+    constexpr double e = -kGp1Over2 / kGamma;
+    return pow(pa / p_b, e) / (rho_b * a_b);
+  }
+};
+
+struct Rup {  // (rho, u, p) on the t-axis
+  double rho, u, p;
+};
+
+MCFD_HD Rup InsideExpansion(double gri_1, double gri_2) {  // exact.hpp:255-266
+  constexpr double r = kGm1 / (kGamma + 1);
+  double a = r * gri_2;
+  double a2 = a * a;
+  double rho = pow(a2 / gri_1 * kOneOverGamma, kOneOverGm1);
+  return Rup{rho, a, a2 * rho * kOneOverGamma};
+}
+
+template <int kField>
+MCFD_HD Rup NearShock(double rb, double ub, double pb, double us, double ps) {
+  // exact.hpp:203-234
+  double divisor = (us - ub) * rb;
+  double shock_u = ub + (divisor != 0 ? (ps - pb) / divisor : ub);
+  bool after = (kField == 1) ? (shock_u < 0) : (shock_u > 0);
+  if (after) {
+    double rho = rb * ((ub - shock_u) / (us - shock_u));
+    return Rup{rho, us, ps};
+  }
+  return Rup{rb, ub, pb};
+}
+
+template <int kField>
+MCFD_HD Rup NearExpansion(double rb, double ub, double pb, double us, double ps) {
+  // exact.hpp:236-292
+  double a_before = SoundSpeed(rb, pb);
+  double a_after = (kField == 1) ? a_before + kGm1Over2 * (ub - us) : a_before - kGm1Over2 * (ub - us);
+  bool after = (kField == 1) ? (us - a_after < 0) : (us + a_after > 0);
+  if (after) {
+    return Rup{kGamma * ps / (a_after * a_after), us, ps};
+  }
+  bool before = (kField == 1) ? (ub - a_before > 0) : (ub + a_before < 0);
+  if (before) {
+    return Rup{rb, ub, pb};
+  }
+  double gri_1 = pb / pow(rb, kGamma);
+  double gri_2 = (kField == 1) ? ub + kGm1Under2 * a_before : ub - kGm1Under2 * a_before;
+  return InsideExpansion(gri_1, gri_2);
+}
+
+// Returns the t-axis state; *star_u receives the contact speed used to upwind the passive
+// (tangential) velocity.  The reference keeps star_u as mutable solver state that is only written
+// in the ordinary (non-vacuum) case (exact.hpp:29, 120); a freshly constructed solver has 0, which
+// is what the vacuum branches see here.
+MCFD_HD Rup SolveExactAxis(double rl, double ul, double pl,
+    double rr, double ur, double pr, double *star_u) {
+  *star_u = 0.0;
+  if (rl > 0) {
+    if (!(rr > 0)) {  // only right vacuum (exact.hpp:68-83)
+      double al = SoundSpeed(rl, pl);
+      if (ul >= al) return Rup{rl, ul, pl};
+      double us = ul + al * kGm1Under2;
+      if (us <= 0) return Rup{0, 0, 0};
+      return InsideExpansion(pl / pow(rl, kGamma), us);
+    }
+  } else {
+    if (rr > 0) {  // only left vacuum (exact.hpp:85-98)
+      double ar = SoundSpeed(rr, pr);
+      if (ur + ar <= 0) return Rup{rr, ur, pr};
+      double us = ur - ar * kGm1Under2;
+      if (us >= 0) return Rup{0, 0, 0};
+      return InsideExpansion(pr / pow(rr, kGamma), us);
+    }
+    return Rup{0, 0, 0};
+  }
+  double du = ur - ul;
+  SpeedChange cl(rl, pl), cr(rr, pr);
+  if (cl.Value(0.0) + cr.Value(0.0) + du < 0) {  // ordinary case (exact.hpp:115-133)
+    // FindRoot (exact.hpp:140-152), eps = 1e-8
+    double x = pl;
+    double fx = cl.Value(x) + cr.Value(x) + du;
+    while (fx > 0) {
+      x *= 0.5;
+      fx = cl.Value(x) + cr.Value(x) + du;
+    }
+    while (fx < -1e-8) {
+      x -= fx / (cl.Prime(x) + cr.Prime(x));
+      fx = cl.Value(x) + cr.Value(x) + du;
+    }
+    double ps = x;
+    double us = 0.5 * (ur + cr.Value(ps) + ul - cl.Value(ps));
+    *star_u = us;
+    if (0 < us) {
+      return (ps >= pl) ? NearShock<1>(rl, ul, pl, us, ps) : NearExpansion<1>(rl, ul, pl, us, ps);
+    }
+    return (ps >= pr) ? NearShock<3>(rr, ur, pr, us, ps) : NearExpansion<3>(rr, ur, pr, us, ps);
+  }
+  // vacuum between wave 1 and wave 3 (exact.hpp:293-320)
+  double al = SoundSpeed(rl, pl);
+  if (ul > al) return Rup{rl, ul, pl};
+  double ar = SoundSpeed(rr, pr);
+  if (ur + ar < 0) return Rup{rr, ur, pr};
+  double gri_1 = pl / pow(rl, kGamma);
+  double gri_2 = ul + al * kGm1Under2;
+  if (gri_2 >= 0) return InsideExpansion(gri_1, gri_2);
+  gri_1 = pr / pow(rr, kGamma);
+  gri_2 = ur - ar * kGm1Under2;
+  if (gri_2 < 0) return InsideExpansion(gri_1, gri_2);
+  return Rup{0, 0, 0};
+}
+
+MCFD_HD NormalFlux SolveExact(double rl, double ul, double pl, double vt2l,
+    double rr, double ur, double pr, double vt2r) {
+  double star_u;
+  Rup s = SolveExactAxis(rl, ul, pl, rr, ur, pr, &star_u);
+  bool from_left = star_u > 0;  // SetPassiveScalars (exact.hpp:56-60)
+  double vt2 = from_left ? vt2l : vt2r;
+  double ke = 0.5 * (s.u * s.u + vt2);
+  NormalFlux f;
+  StateFlux(s.rho, s.u, s.p, ke, &f.mass, &f.mom_n, &f.energy);
+  f.c_left = from_left ? f.mass : 0.0;
+  f.c_right = from_left ? 0.0 : f.mass;
+  return f;
+}
+
+// rotated::Euler::GetFluxUpwind (rotated/euler.hpp:153-159): conservative states in, global flux out,
+// along the unit normal n (pointing left -> right).
+template <int kRiemann>
+MCFD_HD void FluxUpwind(const double *ul, const double *ur,
+    double nx, double ny, double nz, double *flux) {
+  Prim l = ConsToPrim(ul[0], ul[1], ul[2], ul[3], ul[4]);
+  Prim r = ConsToPrim(ur[0], ur[1], ur[2], ur[3], ur[4]);
+  double unl = l.u * nx + l.v * ny + l.w * nz;
+  double unr = r.u * nx + r.v * ny + r.w * nz;
+  double tlx = l.u - unl * nx, tly = l.v - unl * ny, tlz = l.w - unl * nz;
+  double trx = r.u - unr * nx, try_ = r.v - unr * ny, trz = r.w - unr * nz;
+  NormalFlux f;
+  if (kRiemann == kExact) {
+    f = SolveExact(l.rho, unl, l.p, tlx * tlx + tly * tly + tlz * tlz,
+                   r.rho, unr, r.p, trx * trx + try_ * try_ + trz * trz);
+  } else {
+    double kel = 0.5 * (l.u * l.u + l.v * l.v + l.w * l.w);
+    double ker = 0.5 * (r.u * r.u + r.v * r.v + r.w * r.w);
+    f = (kRiemann == kHllc) ? SolveHllc(l.rho, unl, l.p, kel, r.rho, unr, r.p, ker)
+                            : SolveAusm(l.rho, unl, l.p, kel, r.rho, unr, r.p, ker);
+  }
+  flux[0] = f.mass;
+  flux[1] = f.mom_n * nx + f.c_left * tlx + f.c_right * trx;
+  flux[2] = f.mom_n * ny + f.c_left * tly + f.c_right * try_;
+  flux[3] = f.mom_n * nz + f.c_left * tlz + f.c_right * trz;
+  flux[4] = f.energy;
+}
+
+// Flux of one primitive state along n: GlobalPrimitiveToGlobalFlux (rotated/euler.hpp:68-73).
+MCFD_HD void PrimFluxAlong(const Prim &q, double nx, double ny, double nz,
+    double *flux) {
+  double un = q.u * nx + q.v * ny + q.w * nz;
+  double ke = 0.5 * (q.u * q.u + q.v * q.v + q.w * q.w);
+  double e = q.p * kOneOverGm1 + q.rho * ke;
+  double m = q.rho * un;
+  flux[0] = m;
+  flux[1] = m * q.u + q.p * nx;
+  flux[2] = m * q.v + q.p * ny;
+  flux[3] = m * q.w + q.p * nz;
+  flux[4] = e * un + q.p * un;
+}
+
+enum : int {
+  kBcWall = 0, kBcSupOut = 1, kBcSupIn = 2, kBcSubIn = 3, kBcSubOut = 4, kBcSmart = 5, kBcNoSlip = 6
+};
+
+// Boundary flux along the outward unit normal (rotated/euler.hpp:144-174, 181-236, 260-280, 296-299).
+// `given` is the pre-sampled value of the boundary function at this flux point.
+template <int kRiemann>
+MCFD_HD void BoundaryFlux(int kind, const double *ui, const double *given,
+    double nx, double ny, double nz, double *flux) {
+  switch (kind) {
+  case kBcWall: {
+    Prim q = ConsToPrim(ui[0], ui[1], ui[2], ui[3], ui[4]);
+    flux[0] = 0; flux[1] = q.p * nx; flux[2] = q.p * ny; flux[3] = q.p * nz; flux[4] = 0;
+    break;
+  }
+  case kBcSupOut: {
+    Prim q = ConsToPrim(ui[0], ui[1], ui[2], ui[3], ui[4]);
+    PrimFluxAlong(q, nx, ny, nz, flux);
+    break;
+  }
+  case kBcSupIn: {
+    Prim q = ConsToPrim(given[0], given[1], given[2], given[3], given[4]);
+    PrimFluxAlong(q, nx, ny, nz, flux);
+    break;
+  }
+  case kBcSubIn: {  // Carlson (2011) 2.7, rotated/euler.hpp:181-236
+    Prim q = ConsToPrim(ui[0], ui[1], ui[2], ui[3], ui[4]);
+    double c_int = SoundSpeed(q.rho, q.p);
+    double un = q.u * nx + q.v * ny + q.w * nz;
+    double riemann_int = -un - c_int * kGm1Under2;
+    double u_cos = given[1], v_cos = given[2], w_cos = given[3], t_total = given[4];
+    double a_dir = nx * u_cos + ny * v_cos + nz * w_cos;
+    double a2 = a_dir * a_dir;
+    const double gamma_r = kGamma * kGasR;
+    double qa = a2 + kGm1Under2;
+    double qb_half = riemann_int;
+    double qc = kGm1Over2 * (riemann_int * riemann_int) - a2 * gamma_r * t_total;
+    double sqrt_delta = sqrt(qb_half * qb_half - qa * qc);
+    double c_b = fmax((-qb_half + sqrt_delta) / qa, (-qb_half - sqrt_delta) / qa);
+    double t_b = c_b * c_b / gamma_r;
+    double mach_b = sqrt((t_total / t_b - 1) / kGm1Over2);
+    double p_b = given[0] / pow(1 + kGm1Over2 * mach_b * mach_b, kGammaOverGm1);
+    double speed = mach_b * c_b;
+    Prim b;
+    b.p = p_b;
+    b.rho = p_b / kGasR / t_b;
+    b.u = u_cos * speed; b.v = v_cos * speed; b.w = w_cos * speed;
+    PrimFluxAlong(b, nx, ny, nz, flux);
+    break;
+  }
+  case kBcSubOut: {  // Carlson (2011) 2.4, rotated/euler.hpp:260-280
+    Prim q = ConsToPrim(ui[0], ui[1], ui[2], ui[3], ui[4]);
+    double rt = q.p / q.rho;
+    q.p = given[4];
+    q.rho = q.p / rt;
+    PrimFluxAlong(q, nx, ny, nz, flux);
+    break;
+  }
+  case kBcSmart:  // early return at rotated/euler.hpp:299
+    FluxUpwind<kRiemann>(ui, given, nx, ny, nz, flux);
+    break;
+  default:  // kBcNoSlip: no-op for inviscid systems (fem.hpp:382-383) -> caller skips
+    flux[0] = flux[1] = flux[2] = flux[3] = flux[4] = 0;
+  }
+}
+
+}  // namespace mcfd
+#endif  // MINICFD_B200_PHYSICS_CUH_
