@@ -1,0 +1,259 @@
+"""ctypes binding of libminicfd_b200.so (include/minicfd_b200.h).  No CPU fallback: importing works
+anywhere, but every compute call needs the built CUDA library and a GPU and raises otherwise."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libminicfd_b200.so")
+
+FR_LOBATTO, DG_LOBATTO = 0, 1
+EXACT, HLLC, AUSM = 0, 1, 2
+(BC_INVISCID_WALL, BC_SUPERSONIC_OUTLET, BC_SUPERSONIC_INLET, BC_SUBSONIC_INLET, BC_SUBSONIC_OUTLET,
+ BC_SMART, BC_NO_SLIP_WALL) = range(7)
+
+TIME_CALLBACK = C.CFUNCTYPE(None, C.c_void_p, C.c_double)
+
+
+class Config(C.Structure):
+    _fields_ = [("scheme", C.c_int32), ("degree", C.c_int32), ("riemann", C.c_int32), ("device", C.c_int32)]
+
+
+class McfdError(RuntimeError):
+    pass
+
+
+_lib = None
+
+# every symbol include/minicfd_b200.h declares: (name, restype, argtypes)
+_P = C.c_void_p
+_D = C.POINTER(C.c_double)
+_I64 = C.POINTER(C.c_int64)
+_I32 = C.POINTER(C.c_int32)
+SYMBOLS = {
+    "mcfd_create": (C.c_int, [C.POINTER(Config), C.POINTER(_P)]),
+    "mcfd_destroy": (C.c_int, [_P]),
+    "mcfd_last_error": (C.c_char_p, [_P]),
+    "mcfd_set_stream": (C.c_int, [_P, _P]),
+    "mcfd_set_mesh": (C.c_int, [_P, C.c_int64, _D, C.c_int64, C.c_int64, _I64, C.c_int64, _I64, _I32,
+                                C.c_int64, _I64]),
+    "mcfd_get_faces": (C.c_int64, [_P, C.c_int, _I64, _I64, _I32, _I32, _I32]),
+    "mcfd_get_cell_geometry": (C.c_int, [_P, _D, _D]),
+    "mcfd_set_halo": (C.c_int, [_P, C.c_int32, _I64, _I64, C.c_int32, _I64, _I64]),
+    "mcfd_halo_buffers": (C.c_int, [_P, C.POINTER(_P), _I64, C.POINTER(_P), _I64]),
+    "mcfd_halo_pack": (C.c_int, [_P]),
+    "mcfd_halo_unpack": (C.c_int, [_P]),
+    "mcfd_set_boundary": (C.c_int, [_P, C.c_int32, C.c_int32]),
+    "mcfd_count_boundary_faces": (C.c_int64, [_P, C.c_int32]),
+    "mcfd_get_boundary_points": (C.c_int, [_P, C.c_int32, _D]),
+    "mcfd_set_boundary_values": (C.c_int, [_P, C.c_int32, _D]),
+    "mcfd_set_time_callback": (C.c_int, [_P, TIME_CALLBACK, _P]),
+    "mcfd_count_local_cells": (C.c_int64, [_P]),
+    "mcfd_cell_data_size": (C.c_int64, [_P]),
+    "mcfd_set_solution": (C.c_int, [_P, _D]),
+    "mcfd_get_solution": (C.c_int, [_P, _D]),
+    "mcfd_set_solution_device": (C.c_int, [_P, _P]),
+    "mcfd_get_solution_device": (C.c_int, [_P, _P]),
+    "mcfd_residual": (C.c_int, [_P, C.c_double, _D, _P]),
+    "mcfd_rk_step": (C.c_int, [_P, C.c_int, C.c_double, C.c_double]),
+    "mcfd_rk_begin": (C.c_int, [_P, C.c_int, C.c_double, C.c_double]),
+    "mcfd_rk_stage_inner": (C.c_int, [_P, C.c_int]),
+    "mcfd_rk_stage_inter": (C.c_int, [_P, C.c_int]),
+    "mcfd_rk_stage_time": (C.c_double, [_P, C.c_int]),
+    "mcfd_time_step": (C.c_int, [_P, C.c_double, C.c_int, _D]),
+    "mcfd_launch_count": (C.c_int64, [_P]),
+    "mcfd_enable_kernel_timing": (C.c_int, [_P, C.c_int]),
+    "mcfd_kernel_time": (C.c_int, [_P, _D, _I64, C.c_int]),
+    "mcfd_riemann_flux": (C.c_int, [_P, C.c_int32, C.c_int64, _D, _D, _D, _D]),
+}
+
+
+def load():
+    """Load the CUDA library; raises McfdError when it has not been built (no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise McfdError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'`"
+                            " (there is no CPU fallback)")
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def _dp(a):
+    return None if a is None else a.ctypes.data_as(_D)
+
+
+def _ip(a):
+    return None if a is None else a.ctypes.data_as(_I64)
+
+
+def _i32(a):
+    return None if a is None else a.ctypes.data_as(_I32)
+
+
+class Context:
+    """One mcfd_ctx: a part of the mesh resident on one GPU."""
+
+    def __init__(self, scheme=FR_LOBATTO, degree=2, riemann=HLLC, device=-1):
+        self.lib = load()
+        self.h = _P()
+        cfg = Config(scheme, degree, riemann, device)
+        rc = self.lib.mcfd_create(C.byref(cfg), C.byref(self.h))
+        if rc != 0:
+            raise McfdError(f"mcfd_create failed ({rc}): {self.lib.mcfd_last_error(None).decode()}")
+        self.degree = degree
+        self.q = degree + 1
+        self.kfields = 5 * self.q ** 3
+        self.n_local = 0
+        self._cb = None
+
+    def _check(self, rc):
+        if rc != 0:
+            raise McfdError(f"libminicfd_b200 error {rc}: {self.lib.mcfd_last_error(self.h).decode()}")
+
+    def close(self):
+        if self.h:
+            self.lib.mcfd_destroy(self.h)
+            self.h = _P()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_stream(self, cuda_stream: int):
+        self._check(self.lib.mcfd_set_stream(self.h, _P(cuda_stream)))
+
+    def set_mesh(self, nodes, cell_nodes, n_local, n_ghost, bface_nodes, bface_tags, periodic=None):
+        nodes = np.ascontiguousarray(nodes, dtype=np.float64)
+        cell_nodes = np.ascontiguousarray(cell_nodes, dtype=np.int64)
+        bface_nodes = np.ascontiguousarray(bface_nodes, dtype=np.int64).reshape(-1, 4)
+        bface_tags = np.ascontiguousarray(bface_tags, dtype=np.int32)
+        assert cell_nodes.shape == (n_local + n_ghost, 8)
+        pairs = None if periodic is None else np.ascontiguousarray(periodic, dtype=np.int64)
+        self._check(self.lib.mcfd_set_mesh(self.h, len(nodes), _dp(nodes), n_local, n_ghost, _ip(cell_nodes),
+                                           len(bface_nodes), _ip(bface_nodes), _i32(bface_tags),
+                                           0 if pairs is None else len(pairs), _ip(pairs)))
+        self.n_local = n_local
+
+    def faces(self, kind):
+        n = self.lib.mcfd_get_faces(self.h, kind, None, None, None, None, None)
+        if n < 0:
+            self._check(int(n))
+        holder = np.empty(n, dtype=np.int64); sharer = np.empty(n, dtype=np.int64)
+        hf = np.empty(n, dtype=np.int32); sf = np.empty(n, dtype=np.int32); o = np.empty(n, dtype=np.int32)
+        self.lib.mcfd_get_faces(self.h, kind, _ip(holder), _ip(sharer), _i32(hf), _i32(sf), _i32(o))
+        return holder, sharer, hf, sf, o
+
+    def cell_geometry(self):
+        length = np.empty(self.n_local); volume = np.empty(self.n_local)
+        self._check(self.lib.mcfd_get_cell_geometry(self.h, _dp(length), _dp(volume)))
+        return length, volume
+
+    def set_halo(self, send_counts, send_cells, recv_counts, recv_cells):
+        sc = np.ascontiguousarray(send_counts, dtype=np.int64); scl = np.ascontiguousarray(send_cells, dtype=np.int64)
+        rc = np.ascontiguousarray(recv_counts, dtype=np.int64); rcl = np.ascontiguousarray(recv_cells, dtype=np.int64)
+        self._check(self.lib.mcfd_set_halo(self.h, len(sc), _ip(sc), _ip(scl), len(rc), _ip(rc), _ip(rcl)))
+
+    def halo_buffers(self):
+        sp, rp = _P(), _P()
+        sn, rn = C.c_int64(), C.c_int64()
+        self._check(self.lib.mcfd_halo_buffers(self.h, C.byref(sp), C.byref(sn), C.byref(rp), C.byref(rn)))
+        return (sp.value or 0, sn.value), (rp.value or 0, rn.value)
+
+    def halo_pack(self):
+        self._check(self.lib.mcfd_halo_pack(self.h))
+
+    def halo_unpack(self):
+        self._check(self.lib.mcfd_halo_unpack(self.h))
+
+    def set_boundary(self, tag, kind):
+        self._check(self.lib.mcfd_set_boundary(self.h, tag, kind))
+
+    def boundary_points(self, tag):
+        n = self.lib.mcfd_count_boundary_faces(self.h, tag)
+        if n < 0:
+            self._check(int(n))
+        xyz = np.empty((n, self.q * self.q, 3))
+        if n:
+            self._check(self.lib.mcfd_get_boundary_points(self.h, tag, _dp(xyz)))
+        return xyz
+
+    def set_boundary_values(self, tag, values):
+        values = np.ascontiguousarray(values, dtype=np.float64)
+        if values.size:
+            self._check(self.lib.mcfd_set_boundary_values(self.h, tag, _dp(values)))
+
+    def set_time_callback(self, fn):
+        """fn(t) is called before every residual evaluation."""
+        if fn is None:
+            self._cb = C.cast(None, TIME_CALLBACK)
+        else:
+            self._cb = TIME_CALLBACK(lambda user, t: fn(t))
+        self._check(self.lib.mcfd_set_time_callback(self.h, self._cb, None))
+
+    def set_solution(self, column):
+        column = np.ascontiguousarray(column, dtype=np.float64)
+        assert column.size == self.n_local * self.kfields
+        self._check(self.lib.mcfd_set_solution(self.h, _dp(column)))
+
+    def get_solution(self, out=None):
+        out = np.empty(self.n_local * self.kfields) if out is None else out
+        self._check(self.lib.mcfd_get_solution(self.h, _dp(out)))
+        return out
+
+    def set_solution_device(self, ptr: int):
+        self._check(self.lib.mcfd_set_solution_device(self.h, _P(ptr)))
+
+    def get_solution_device(self, ptr: int):
+        self._check(self.lib.mcfd_get_solution_device(self.h, _P(ptr)))
+
+    def residual(self, t=0.0, out=None):
+        out = np.empty(self.n_local * self.kfields) if out is None else out
+        self._check(self.lib.mcfd_residual(self.h, t, _dp(out), None))
+        return out
+
+    def rk_step(self, order, t, dt):
+        self._check(self.lib.mcfd_rk_step(self.h, order, t, dt))
+
+    def rk_begin(self, order, t, dt):
+        self._check(self.lib.mcfd_rk_begin(self.h, order, t, dt))
+
+    def rk_stage_inner(self, stage):
+        self._check(self.lib.mcfd_rk_stage_inner(self.h, stage))
+
+    def rk_stage_inter(self, stage):
+        self._check(self.lib.mcfd_rk_stage_inter(self.h, stage))
+
+    def time_step(self, dt_guess, rk_order):
+        dt = C.c_double()
+        self._check(self.lib.mcfd_time_step(self.h, dt_guess, rk_order, C.byref(dt)))
+        return dt.value
+
+    def launch_count(self):
+        return int(self.lib.mcfd_launch_count(self.h))
+
+    def enable_kernel_timing(self, on=True):
+        self._check(self.lib.mcfd_enable_kernel_timing(self.h, int(on)))
+
+    def kernel_time(self, reset=True):
+        ms, n = C.c_double(), C.c_int64()
+        self._check(self.lib.mcfd_kernel_time(self.h, C.byref(ms), C.byref(n), int(reset)))
+        return ms.value, n.value
+
+    def riemann_flux(self, normals, ul, ur, bc_kind=-1):
+        normals = np.ascontiguousarray(normals, dtype=np.float64).reshape(-1, 3)
+        ul = np.ascontiguousarray(ul, dtype=np.float64).reshape(-1, 5)
+        ur = np.ascontiguousarray(ur, dtype=np.float64).reshape(-1, 5)
+        out = np.empty_like(ul)
+        self._check(self.lib.mcfd_riemann_flux(self.h, bc_kind, len(ul), _dp(normals), _dp(ul), _dp(ur), _dp(out)))
+        return out

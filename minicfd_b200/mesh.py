@@ -35,7 +35,7 @@ class HexMesh:
 
 def box(nx: int, ny: int, nz: int, lo=(0.0, 0.0, 0.0), hi=(1.0, 1.0, 1.0), *, warp: float = 0.0,
         seed: int = 0, periodic: bool = False) -> HexMesh:
-    """nx*ny*nz Hexahedron8 cells; cell id = (ix*ny + iy)*nz + iz... no: x fastest (ix + nx*(iy + ny*iz)).
+    """nx*ny*nz Hexahedron8 cells, cell id = ix + nx*(iy + ny*iz).
 
     warp > 0 displaces interior nodes by warp*h uniformly at random (non-affine cells).
     periodic=True emits no boundary faces but `periodic` face pairs instead (GPU-only variant, the
@@ -83,8 +83,13 @@ def box(nx: int, ny: int, nz: int, lo=(0.0, 0.0, 0.0), hi=(1.0, 1.0, 1.0), *, wa
     mesh = HexMesh(nodes=nodes, cells=cells, bfaces=np.concatenate(bf), btags=np.concatenate(bt),
                    dims=(nx, ny, nz))
     if periodic:
-        for lo_tag, hi_tag in ((XMIN, XMAX), (YMIN, YMAX), (ZMIN, ZMAX)):
-            pairs.append(np.stack([quads[lo_tag], quads[hi_tag]], axis=1))
+        # vertex m of the low-side quad coincides (up to the period) with vertex m of the high-side one
+        matched = {XMAX: [1, 5, 6, 2], YMAX: [3, 2, 6, 7], ZMAX: [4, 7, 6, 5]}
+        for (lo_tag, hi_tag), (tag, lf, cfun, (na, nb)) in zip(((XMIN, XMAX), (YMIN, YMAX), (ZMIN, ZMAX)),
+                                                              (sides[1], sides[3], sides[5])):
+            b, a = np.meshgrid(np.arange(nb), np.arange(na), indexing="ij")
+            hi_quads = cells[cfun(a.ravel(), b.ravel())][:, matched[hi_tag]]
+            pairs.append(np.stack([quads[lo_tag], hi_quads], axis=1))
         mesh.periodic = np.concatenate(pairs).astype(np.int64)
         mesh.bfaces = np.zeros((0, 4), dtype=np.int64)
         mesh.btags = np.zeros((0,), dtype=np.int32)

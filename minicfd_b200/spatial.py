@@ -1,0 +1,161 @@
+"""Host-side mirror of the reference's operator interface for the hot path, over the C ABI.
+
+`Spatial` plays the role of `mini::spatial::fr::Lobatto<Part, Riemann>` / `dg::Lobatto<Part, Riemann>`
+as a `mini::temporal::System` (include/mini/spatial/fem.hpp:47-436, include/mini/temporal/ode.hpp:17-48):
+same method names, argument meaning and call order, so that the parity tests read like the reference's
+own tests (test/spatial/fr.cpp).  All arithmetic happens in libminicfd_b200.so on the GPU.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import capi
+from .part import Part, cell_points
+
+
+class Spatial:
+    def __init__(self, part: Part, *, scheme=capi.FR_LOBATTO, degree=2, riemann=capi.HLLC, device=-1,
+                 comm=None):
+        self.part = part
+        self.degree = degree
+        self.ctx = capi.Context(scheme, degree, riemann, device)
+        self.kfields = self.ctx.kfields
+        m = part.mesh
+        self.ctx.set_mesh(m.nodes, part.cell_nodes, part.n_local, part.n_ghost, part.bfaces, part.btags,
+                          m.periodic)
+        if part.n_ghost:
+            self.ctx.set_halo([len(c) for c in part.send_cells],
+                              np.concatenate(part.send_cells) if part.send_cells else [],
+                              [len(c) for c in part.recv_cells],
+                              np.concatenate(part.recv_cells) if part.recv_cells else [])
+        self.comm = comm            # halo exchanger (minicfd_b200.halo) or None for a single part
+        if comm is not None:
+            comm.attach(self)
+        self._bc_funcs = {}         # tag -> (kind, func or None, time_dependent)
+        self._bc_points = {}
+        self._t = 0.0
+        self.ctx.set_time_callback(self._on_time)
+
+    # ---- mini::spatial::FiniteElement (fem.hpp:128-154, 196-222) ---------------------------------
+    def name(self):
+        return "FR::Lobatto" if self.ctx is not None else ""
+
+    def part_ptr(self):
+        return self.part
+
+    def Approximate(self, func):
+        """fem.hpp:147-154: nodal sampling of func(xyz) on every local cell, then a halo exchange."""
+        pts = cell_points(self.part.mesh.nodes, self.part.cell_nodes[:self.part.n_local], self.degree)
+        vals = np.asarray(func(pts))
+        self.SetSolutionColumn(vals.reshape(-1))
+
+    def _set_bc(self, tag, kind, func=None, time_dependent=True):
+        self.ctx.set_boundary(tag, kind)
+        self._bc_funcs[tag] = (kind, func, time_dependent)
+        if func is not None:
+            self._bc_points[tag] = self.ctx.boundary_points(tag)
+            self.ctx.set_boundary_values(tag, func(self._bc_points[tag], self._t))
+
+    def SetSmartBoundary(self, tag, func, time_dependent=True):
+        self._set_bc(tag, capi.BC_SMART, func, time_dependent)
+
+    def SetSupersonicInlet(self, tag, func, time_dependent=True):
+        self._set_bc(tag, capi.BC_SUPERSONIC_INLET, func, time_dependent)
+
+    def SetSubsonicInlet(self, tag, func, time_dependent=True):
+        self._set_bc(tag, capi.BC_SUBSONIC_INLET, func, time_dependent)
+
+    def SetSubsonicOutlet(self, tag, func, time_dependent=True):
+        self._set_bc(tag, capi.BC_SUBSONIC_OUTLET, func, time_dependent)
+
+    def SetNoSlipWall(self, tag, func=None, time_dependent=False):
+        self._set_bc(tag, capi.BC_NO_SLIP_WALL, None, False)
+
+    def SetInviscidWall(self, tag):
+        self._set_bc(tag, capi.BC_INVISCID_WALL)
+
+    def SetSupersonicOutlet(self, tag):
+        self._set_bc(tag, capi.BC_SUPERSONIC_OUTLET)
+
+    def _on_time(self, t):
+        """Re-sample time-dependent boundary functions (the reference evaluates its std::function at
+        (xyz, t_curr_) inside the face loops, fr/lobatto.hpp:350)."""
+        self._t = t
+        for tag, (kind, func, time_dependent) in self._bc_funcs.items():
+            if func is not None and time_dependent:
+                self.ctx.set_boundary_values(tag, func(self._bc_points[tag], t))
+
+    # ---- mini::temporal::System (ode.hpp:17-48; fem.hpp:225-258) -----------------------------------
+    def SetTime(self, t):
+        self._t = t
+
+    def SetSolutionColumn(self, column):
+        self.ctx.set_solution(column)
+
+    def GetSolutionColumn(self):
+        return self.ctx.get_solution()
+
+    def GetResidualColumn(self):
+        """fem.hpp:248-258: halo exchange, then volume + face + boundary terms (one fused kernel)."""
+        if self.comm is not None:
+            self.comm.exchange()
+        return self.ctx.residual(self._t)
+
+    def GetTimeStep(self, dt_guess, rk_order):
+        """fem.hpp:417-435 / fr/lobatto.hpp:220-222, then MPI_Allreduce(MIN) as in sourceless.cpp:194."""
+        dt = self.ctx.time_step(dt_guess, rk_order)
+        if self.comm is not None:
+            dt = self.comm.allreduce_min(dt)
+        return dt
+
+
+class RungeKutta:
+    """mini::temporal::RungeKutta<kOrders> (include/mini/temporal/rk.hpp:10-57).  `Update` uses the
+    fused stage kernels (mcfd_rk_*); `UpdateGeneric` spells the reference's column algebra out through
+    the System interface and is used by tests to check the fused path against it."""
+
+    def __init__(self, order):
+        assert order in (1, 2, 3)
+        self.order = order
+
+    def Update(self, system: Spatial, t, dt):
+        ctx = system.ctx
+        if system.comm is None:
+            ctx.rk_step(self.order, t, dt)
+            return
+        ctx.rk_begin(self.order, t, dt)
+        for stage in range(self.order):
+            system.comm.start()            # pack + post sends/recvs (ShareGhostCellCoeffs)
+            ctx.rk_stage_inner(stage)      # overlaps the exchange (fem.hpp:249-254)
+            system.comm.finish()           # wait + unpack (UpdateGhostCellCoeffs)
+            ctx.rk_stage_inter(stage)
+
+    def UpdateGeneric(self, system: Spatial, t, dt):
+        def euler_next(tt):
+            system.SetTime(tt)
+            u = system.GetSolutionColumn()
+            r = system.GetResidualColumn()
+            r *= dt
+            u += r
+            return u
+        if self.order == 1:
+            system.SetSolutionColumn(euler_next(t))
+        elif self.order == 2:
+            u0 = system.GetSolutionColumn()
+            system.SetSolutionColumn(euler_next(t))
+            u = euler_next(t + dt)
+            u += u0
+            u *= 0.5
+            system.SetSolutionColumn(u)
+        else:
+            u0 = system.GetSolutionColumn()
+            system.SetSolutionColumn(euler_next(t))
+            u = u0 * 3
+            u += euler_next(t + dt)
+            u /= 4
+            system.SetSolutionColumn(u)
+            u = euler_next(t + dt / 2)
+            u *= 2
+            u += u0
+            u /= 3
+            system.SetSolutionColumn(u)

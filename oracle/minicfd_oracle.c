@@ -1,0 +1,726 @@
+/* TEST INFRASTRUCTURE — NOT PART OF THE PRODUCT PATH.
+ *
+ * minicfd_oracle.c: a plain-C, single-threaded restatement of the reference's algorithm for the hot
+ * path (pvcStillinGradSchool/miniCFD @ e14f896): FR-Lobatto / DG-Lobatto Euler residual on
+ * Hexahedron8 cells, Exact / HLLC / AUSM Riemann solvers, the inviscid boundary kinds, RK1/2/3 and the
+ * CFL time step.  It is deliberately written the way the reference works — face loops that scatter to
+ * holder and sharer, flux points matched to solution points by COORDINATES, the Riemann problem solved
+ * in the rotated (normal, tangent, bitangent) frame, dense volume loops — and not the way the CUDA
+ * kernels work, so that the two are independent.  Citations are paths under the reference's
+ * include/mini/ unless stated otherwise.
+ *
+ * PINNED: tests/test_oracle_pinned.py checks this file against the reference's own code compiled from
+ * /root/reference (oracle/_ref via ref_harness.cpp) and against the golden vectors under
+ * tests/golden/ generated from it (tests/golden/make_golden.py), and the Riemann solvers against the
+ * Toro known-answer states the reference's tests use (test/riemann/euler/exact.cpp:57-138).
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may load this library.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define GAMMA 1.4
+#define GAS_R 287.05
+#define MAXQ 4
+#define MAXN 64
+
+/* ---- riemann/euler/types.hpp ----------------------------------------------------------------- */
+typedef struct { double rho, u, v, w, p; } prim_t;
+
+static prim_t cons_to_prim(const double *c) { /* types.hpp:289-301 with :194-202 */
+  prim_t q = {c[0], c[1], c[2], c[3], c[4]};
+  if (q.rho < 0) memset(&q, 0, sizeof q);
+  if (q.p < 0) memset(&q, 0, sizeof q);
+  if (q.rho != 0) {
+    q.u /= q.rho; q.v /= q.rho; q.w /= q.rho;
+    q.p -= q.rho * (0.5 * (q.u * q.u + q.v * q.v + q.w * q.w));
+    q.p *= GAMMA - 1;
+    if (q.rho < 0) memset(&q, 0, sizeof q);
+    if (q.p < 0) memset(&q, 0, sizeof q);
+  }
+  return q;
+}
+static double sound_speed(double rho, double p) { /* types.hpp:252-254 */
+  return (rho > 0 && p > 0) ? sqrt(GAMMA * p / rho) : 0;
+}
+static void prim_to_flux(const prim_t *q, double *f) { /* types.hpp:313-320 */
+  double ke = 0.5 * (q->u * q->u + q->v * q->v + q->w * q->w);
+  double c[5] = {q->rho, q->rho * q->u, q->rho * q->v, q->rho * q->w, q->p * (1 / (GAMMA - 1)) + q->rho * ke};
+  for (int k = 0; k < 5; ++k) f[k] = c[k] * q->u;
+  f[1] += q->p;
+  f[4] += q->p * q->u;
+}
+static void flux_matrix(const double *c, double m[5][3]) { /* types.hpp:322-333 */
+  prim_t q = cons_to_prim(c);
+  double vel[3] = {q.u, q.v, q.w};
+  double h0 = c[4] + q.p;
+  for (int d = 0; d < 3; ++d) {
+    m[0][d] = c[1 + d];
+    m[1][d] = c[1] * vel[d];
+    m[2][d] = c[2] * vel[d];
+    m[3][d] = c[3] * vel[d];
+    m[1 + d][d] += q.p;
+    m[4][d] = h0 * vel[d];
+  }
+}
+
+/* ---- riemann/euler/hllc.hpp -------------------------------------------------------------------- */
+static double hllc_q(double pe, double pk) { /* hllc.hpp:69-77 */
+  if (pe <= pk) return 1.0;
+  return sqrt(1 + ((GAMMA + 1) / 2) * (pe / pk - 1) / GAMMA);
+}
+static void hllc_star(const prim_t *s, double wk, double ws, double *f) { /* hllc.hpp:94-109 */
+  prim_to_flux(s, f);
+  double ke = 0.5 * (s->u * s->u + s->v * s->v + s->w * s->w);
+  double uk[5] = {s->rho, s->rho * s->u, s->rho * s->v, s->rho * s->w, s->p * (1 / (GAMMA - 1)) + s->rho * ke};
+  double temp = s->rho * (wk - s->u) / (wk - ws);
+  double us[5] = {temp, temp * ws, temp * s->v, temp * s->w, 0};
+  us[4] = uk[4] / s->rho + (ws - s->u) * (ws + s->p / (s->rho * (wk - s->u)));
+  us[4] *= temp;
+  for (int k = 0; k < 5; ++k) f[k] += (us[k] - uk[k]) * wk;
+}
+static void hllc(const prim_t *l, const prim_t *r, double *f) { /* hllc.hpp:30-68 */
+  double rho_avg = (l->rho + r->rho) / 2;
+  double al = sound_speed(l->rho, l->p), ar = sound_speed(r->rho, r->p);
+  double a_avg = (al + ar) / 2;
+  double p_pvrs = (l->p + r->p - (r->u - l->u) * rho_avg * a_avg) / 2;
+  double pe = p_pvrs > 0 ? p_pvrs : 0;
+  double wl = l->u - al * hllc_q(pe, l->p);
+  double wr = r->u + ar * hllc_q(pe, r->p);
+  double ws = (r->p - l->p + l->rho * l->u * (wl - l->u) - r->rho * r->u * (wr - r->u)) /
+              (l->rho * (wl - l->u) - r->rho * (wr - r->u));
+  if (0.0 <= wl) prim_to_flux(l, f);
+  else if (wr <= 0.0) prim_to_flux(r, f);
+  else if (0.0 <= ws) hllc_star(l, wl, ws, f);
+  else hllc_star(r, wr, ws, f);
+}
+
+/* ---- riemann/euler/ausm.hpp -------------------------------------------------------------------- */
+static void ausm_signed(const prim_t *s, int negative, double *f) { /* ausm.hpp:52-71 */
+  double a = sound_speed(s->rho, s->p);
+  double h = a * a / (GAMMA - 1) + 0.5 * (s->u * s->u + s->v * s->v + s->w * s->w);
+  double fl[5] = {1, s->u, s->v, s->w, h};
+  double mach = s->u / a, p = s->p;
+  double sm = (1 + (negative ? -mach : mach)) * 0.5;
+  if (mach >= -1 && mach <= 1) {
+    mach = negative ? -(sm * sm) : sm * sm;
+    p *= sm;
+  } else if (sm < 0) {
+    mach = 0; p = 0;
+  }
+  for (int k = 0; k < 5; ++k) f[k] = fl[k] * (s->rho * a * mach);
+  f[1] += p;
+}
+static void ausm(const prim_t *l, const prim_t *r, double *f) { /* ausm.hpp:30-33 */
+  double a[5], b[5];
+  ausm_signed(l, 0, a);
+  ausm_signed(r, 1, b);
+  for (int k = 0; k < 5; ++k) f[k] = a[k] + b[k];
+}
+
+/* ---- riemann/euler/exact.hpp ------------------------------------------------------------------- */
+typedef struct { double rho_b, p_b, a_b, p_const; } speed_change_t;
+static speed_change_t sc_make(const prim_t *b) { /* exact.hpp:155-160 */
+  speed_change_t s = {b->rho, b->p, b->rho == 0 ? 0 : sound_speed(b->rho, b->p), b->p * ((GAMMA - 1) / 2)};
+  return s;
+}
+static double sc_P(const speed_change_t *s, double pa) { return ((GAMMA + 1) / 2) * pa + s->p_const; }
+static double sc_value(const speed_change_t *s, double pa) { /* exact.hpp:161-174 */
+  if (pa >= s->p_b) return (pa - s->p_b) / sqrt(s->rho_b * sc_P(s, pa));
+  double v = pow(pa / s->p_b, ((GAMMA - 1) / 2) / GAMMA) - 1;
+  return v * ((2 / (GAMMA - 1)) * s->a_b);
+}
+static double sc_prime(const speed_change_t *s, double pa) { /* exact.hpp:175-191 */
+  if (pa >= s->p_b) {
+    double p = sc_P(s, pa);
+    double v = ((GAMMA + 1) / 4) * (s->p_b - pa);
+    return (1 + v / p) / sqrt(s->rho_b * p);
+  }
+  return pow(pa / s->p_b, -((GAMMA + 1) / 2) / GAMMA) / (s->rho_b * s->a_b);
+}
+static prim_t inside_expansion(double gri_1, double gri_2) { /* exact.hpp:255-266 */
+  double a = ((GAMMA - 1) / (GAMMA + 1)) * gri_2, a2 = a * a;
+  prim_t x = {0, 0, 0, 0, 0};
+  x.rho = pow(a2 / gri_1 * (1 / GAMMA), 1 / (GAMMA - 1));
+  x.u = a;
+  x.p = a2 * x.rho * (1 / GAMMA);
+  return x;
+}
+static prim_t near_shock(int field, const prim_t *b, prim_t *after) { /* exact.hpp:203-234 */
+  double divisor = (after->u - b->u) * b->rho;
+  double su = b->u + (divisor ? (after->p - b->p) / divisor : b->u);
+  int is_after = field == 1 ? (su < 0) : (su > 0);
+  if (is_after) {
+    after->rho = b->rho * ((b->u - su) / (after->u - su));
+    return *after;
+  }
+  return *b;
+}
+static prim_t near_expansion(int field, const prim_t *b, prim_t *after) { /* exact.hpp:236-292 */
+  double a_before = sound_speed(b->rho, b->p);
+  double gri_1 = b->p / pow(b->rho, GAMMA);
+  double gri_2 = field == 1 ? b->u + (2 / (GAMMA - 1)) * a_before : b->u - (2 / (GAMMA - 1)) * a_before;
+  double a_after = field == 1 ? a_before + ((GAMMA - 1) / 2) * (b->u - after->u)
+                              : a_before - ((GAMMA - 1) / 2) * (b->u - after->u);
+  int t_after = field == 1 ? (after->u - a_after < 0) : (after->u + a_after > 0);
+  if (t_after) {
+    after->rho = GAMMA * after->p / (a_after * a_after);
+    return *after;
+  }
+  int t_before = field == 1 ? (b->u - a_before > 0) : (b->u + a_before < 0);
+  if (t_before) return *b;
+  return inside_expansion(gri_1, gri_2);
+}
+/* exact.hpp:62-138; *star_u as the solver member of :29 (fresh solver: 0) */
+static prim_t exact_axis(const prim_t *l, const prim_t *r, double *star_u) {
+  prim_t zero = {0, 0, 0, 0, 0};
+  if (l->rho > 0) {
+    if (!(r->rho > 0)) {
+      double al = sound_speed(l->rho, l->p);
+      if (l->u >= al) return *l;
+      double us = l->u + al * (2 / (GAMMA - 1));
+      if (us <= 0) return zero;
+      return inside_expansion(l->p / pow(l->rho, GAMMA), us);
+    }
+  } else {
+    if (r->rho > 0) {
+      double ar = sound_speed(r->rho, r->p);
+      if (r->u + ar <= 0) return *r;
+      double us = r->u - ar * (2 / (GAMMA - 1));
+      if (us >= 0) return zero;
+      return inside_expansion(r->p / pow(r->rho, GAMMA), us);
+    }
+    return zero;
+  }
+  double du = r->u - l->u;
+  speed_change_t cl = sc_make(l), cr = sc_make(r);
+#define F_OF(x) (sc_value(&cl, (x)) + sc_value(&cr, (x)) + du)
+  if (F_OF(0.0) < 0) {
+    double x = l->p; /* FindRoot, exact.hpp:140-152 */
+    while (F_OF(x) > 0) x *= 0.5;
+    while (F_OF(x) < -1e-8) x -= F_OF(x) / (sc_prime(&cl, x) + sc_prime(&cr, x));
+    prim_t star = {0, 0, 0, 0, 0};
+    star.p = x;
+    star.u = 0.5 * (r->u + sc_value(&cr, x) + l->u - sc_value(&cl, x));
+    *star_u = star.u;
+    if (0 < star.u) return star.p >= l->p ? near_shock(1, l, &star) : near_expansion(1, l, &star);
+    return star.p >= r->p ? near_shock(3, r, &star) : near_expansion(3, r, &star);
+  }
+#undef F_OF
+  double la = sound_speed(l->rho, l->p); /* PrimitiveNearVacuum, exact.hpp:293-320 */
+  if (l->u > la) return *l;
+  double ra = sound_speed(r->rho, r->p);
+  if (r->u + ra < 0) return *r;
+  double g1 = l->p / pow(l->rho, GAMMA), g2 = l->u + la * (2 / (GAMMA - 1));
+  if (g2 >= 0) return inside_expansion(g1, g2);
+  g1 = r->p / pow(r->rho, GAMMA);
+  g2 = r->u - ra * (2 / (GAMMA - 1));
+  if (g2 < 0) return inside_expansion(g1, g2);
+  return zero;
+}
+static void exact(const prim_t *l, const prim_t *r, double *f) { /* exact.hpp:36-60 */
+  double star_u = 0;
+  prim_t s = exact_axis(l, r, &star_u);
+  s.v = star_u > 0 ? l->v : r->v;
+  s.w = star_u > 0 ? l->w : r->w;
+  prim_to_flux(&s, f);
+}
+
+/* ---- riemann/rotated/euler.hpp ----------------------------------------------------------------- */
+typedef struct { double a[3], b[3], c[3]; } frame_t; /* normal, tangent, bitangent */
+
+static void to_normal(const frame_t *fr, double *m) { /* rotated/euler.hpp:117-125 */
+  double x = m[0], y = m[1], z = m[2];
+  m[0] = x * fr->a[0] + y * fr->a[1] + z * fr->a[2];
+  m[1] = x * fr->b[0] + y * fr->b[1] + z * fr->b[2];
+  m[2] = x * fr->c[0] + y * fr->c[1] + z * fr->c[2];
+}
+static void to_global(const frame_t *fr, double *m) { /* rotated/euler.hpp:126-134 */
+  double a = m[0], b = m[1], c = m[2];
+  m[0] = a * fr->a[0] + b * fr->b[0] + c * fr->c[0];
+  m[1] = a * fr->a[1] + b * fr->b[1] + c * fr->c[1];
+  m[2] = a * fr->a[2] + b * fr->b[2] + c * fr->c[2];
+}
+static void solve_1d(int riemann, const prim_t *l, const prim_t *r, double *f) {
+  if (riemann == 0) exact(l, r, f);
+  else if (riemann == 1) hllc(l, r, f);
+  else ausm(l, r, f);
+}
+static void flux_upwind(int riemann, const frame_t *fr, const double *cl, const double *cr, double *f) {
+  prim_t l = cons_to_prim(cl), r = cons_to_prim(cr); /* rotated/euler.hpp:153-159, 74-88 */
+  to_normal(fr, &l.u);
+  to_normal(fr, &r.u);
+  solve_1d(riemann, &l, &r, f);
+  to_global(fr, &f[1]);
+}
+static void prim_flux_global(const frame_t *fr, prim_t q, double *f) { /* rotated/euler.hpp:68-73 */
+  to_normal(fr, &q.u);
+  prim_to_flux(&q, f);
+  to_global(fr, &f[1]);
+}
+/* kinds: 0 wall 1 supersonic outlet 2 supersonic inlet 3 subsonic inlet 4 subsonic outlet 5 smart */
+static void boundary_flux(int riemann, int kind, const frame_t *fr, const double *ci, const double *given,
+    double *f) {
+  prim_t q;
+  switch (kind) {
+  case 0: /* rotated/euler.hpp:160-174 */
+    q = cons_to_prim(ci);
+    f[0] = 0; f[1] = q.p; f[2] = 0; f[3] = 0; f[4] = 0;
+    to_global(fr, &f[1]);
+    break;
+  case 1: prim_flux_global(fr, cons_to_prim(ci), f); break;    /* :148-151 */
+  case 2: prim_flux_global(fr, cons_to_prim(given), f); break; /* :144-147 */
+  case 3: { /* :181-236 */
+    q = cons_to_prim(ci);
+    double c_int = sound_speed(q.rho, q.p);
+    to_normal(fr, &q.u);
+    double ri = -q.u - c_int * (2 / (GAMMA - 1));
+    double uc = given[1], vc = given[2], wc = given[3], tt = given[4];
+    double A = fr->a[0] * uc + fr->a[1] * vc + fr->a[2] * wc, A2 = A * A, gr = GAMMA * GAS_R;
+    double qa = A2 + 2 / (GAMMA - 1), qb = ri, qc = ((GAMMA - 1) / 2) * (ri * ri) - A2 * gr * tt;
+    double sd = sqrt(qb * qb - qa * qc);
+    double x1 = (-qb + sd) / qa, x2 = (-qb - sd) / qa;
+    double cb = x1 > x2 ? x1 : x2;
+    double tb = cb * cb / gr;
+    double mb = sqrt((tt / tb - 1) / ((GAMMA - 1) / 2));
+    double pb = given[0] / pow(1 + ((GAMMA - 1) / 2) * mb * mb, GAMMA / (GAMMA - 1));
+    double sp = mb * cb;
+    prim_t b = {pb / GAS_R / tb, uc * sp, vc * sp, wc * sp, pb};
+    prim_flux_global(fr, b, f);
+    break;
+  }
+  case 4: { /* :260-280 */
+    q = cons_to_prim(ci);
+    double rt = q.p / q.rho;
+    q.p = given[4];
+    q.rho = q.p / rt;
+    prim_flux_global(fr, q, f);
+    break;
+  }
+  default: flux_upwind(riemann, fr, ci, given, f); /* :296-299 */
+  }
+}
+
+/* ---- fields (same formulas as ref_harness.cpp::EvalField) -------------------------------------- */
+static void eval_field(int kind, const double *prm, const double *x, double t, double *v) {
+  if (kind == 0) {
+    for (int k = 0; k < 5; ++k) v[k] = prm[k];
+  } else if (kind == 1) {
+    const double g = GAMMA, pi = 3.14159265358979323846;
+    double dx = x[0] - prm[0] - prm[2] * t, dy = x[1] - prm[1] - prm[3] * t, beta = prm[5];
+    double e = exp(0.5 * (1 - (dx * dx + dy * dy)));
+    double du = -beta / (2 * pi) * e * dy, dv = beta / (2 * pi) * e * dx;
+    double T = 1 - (g - 1) * beta * beta / (8 * g * pi * pi) * e * e;
+    double rho = pow(T, 1 / (g - 1)), p = pow(rho, g);
+    double u = prm[2] + du, vv = prm[3] + dv, w = prm[4];
+    v[0] = rho; v[1] = rho * u; v[2] = rho * vv; v[3] = rho * w;
+    v[4] = p / (g - 1) + 0.5 * rho * (u * u + vv * vv + w * w);
+  } else {
+    double a = prm[0] ? prm[0] : 1.0;
+    double rho = 1.0 + 0.2 * sin(a * (x[0] + 2 * x[1] - x[2]) + 0.3 * t);
+    double u = 0.5 + 0.3 * cos(a * (x[0] - x[1]) + 0.1);
+    double vv = -0.2 + 0.25 * sin(a * (x[1] + x[2]) + 0.7);
+    double w = 0.1 + 0.2 * cos(a * (x[2] - 2 * x[0]) - 0.4);
+    double p = 1.0 + 0.3 * sin(a * (x[0] + x[1] + x[2]) + 1.1);
+    v[0] = rho; v[1] = rho * u; v[2] = rho * vv; v[3] = rho * w;
+    v[4] = p / 0.4 + 0.5 * rho * (u * u + vv * vv + w * w);
+  }
+}
+
+/* ---- discretisation ------------------------------------------------------------------------------ */
+static const int FACE_NODES[6][4] = { /* coordinate/hexahedron.hpp:378-389 */
+  {0, 3, 2, 1}, {0, 1, 5, 4}, {1, 2, 6, 5}, {2, 3, 7, 6}, {0, 4, 7, 3}, {4, 5, 6, 7}};
+static const double VERT[8][3] = {{-1, -1, -1}, {1, -1, -1}, {1, 1, -1}, {-1, 1, -1},
+                                  {-1, -1, 1}, {1, -1, 1}, {1, 1, 1}, {-1, 1, 1}};
+static const double QUAD[4][2] = {{-1, -1}, {1, -1}, {1, 1}, {-1, 1}};
+
+static void lobatto(int q, double *x, double *w) { /* integrator/lobatto.hpp:38-57 */
+  if (q == 3) { x[0] = -1; x[1] = 0; x[2] = 1; w[0] = 1.0 / 3; w[1] = 4.0 / 3; w[2] = 1.0 / 3; }
+  else { x[0] = -1; x[1] = -sqrt(1.0 / 5); x[2] = sqrt(1.0 / 5); x[3] = 1;
+         w[0] = 1.0 / 6; w[1] = 5.0 / 6; w[2] = 5.0 / 6; w[3] = 1.0 / 6; }
+}
+static double lagrange_d(int q, const double *x, int m, int i) { /* l_m'(x_i), basis/lagrange.hpp:130-133 */
+  double sum = 0;
+  for (int k = 0; k < q; ++k) {
+    if (k == m) continue;
+    double prod = 1.0 / (x[m] - x[k]);
+    for (int l = 0; l < q; ++l) if (l != m && l != k) prod *= (x[i] - x[l]) / (x[m] - x[l]);
+    sum += prod;
+  }
+  return sum;
+}
+static double g_prime_right_at_one(int degree) { /* basis/vincent.hpp:31-33, 75-91 */
+  double cn = degree / (2.0 * degree + 1), cp = 1 - cn, prev = 0, curr = 0, next = 0;
+  for (int k = 0; k <= degree; ++k) {
+    if (k > 0) { prev = curr; curr = next; }
+    next = (k + 1) * 1.0 + 1.0 * curr; /* P_k(1) = 1 */
+  }
+  return 0.5 * (curr + cp * prev + cn * next);
+}
+
+typedef struct {
+  int degree, q, n, scheme, riemann;
+  int64_t n_cells;
+  double x[MAXQ], w[MAXQ], d1[MAXQ][MAXQ]; /* d1[i][m] = l_m'(x_i) */
+  double *xyz;      /* [cell][n][3] node coordinates */
+  double *jstar;    /* [cell][n][3][3]  J*(x, d) */
+  double *jinv;     /* [cell][n][3][3]  J^-1(x, d) */
+  double *det;      /* [cell][n] */
+  double *length;   /* [cell] */
+  /* faces */
+  int64_t n_faces;  /* interior first, then boundary */
+  int64_t n_interior;
+  int64_t *holder, *sharer;
+  int *tag;
+  int *h_node, *s_node;   /* [face][q*q] cell node of each flux point */
+  int *h_dir, *s_dir;     /* [face] direction of the face on each side */
+  double *h_scale, *s_scale; /* [face][q*q] +-|J*.col(d)| */
+  frame_t *frame;         /* [face][q*q] */
+  double *fweight;        /* [face][q*q] global face weight */
+  double *fxyz;           /* [face][q*q][3] */
+  int bc_kind[16], field_kind[16];
+  double field_prm[16][8];
+} oracle_t;
+
+static void cross(const double *a, const double *b, double *c) {
+  c[0] = a[1] * b[2] - a[2] * b[1]; c[1] = a[2] * b[0] - a[0] * b[2]; c[2] = a[0] * b[1] - a[1] * b[0];
+}
+static double norm3(const double *a) { return sqrt(a[0] * a[0] + a[1] * a[1] + a[2] * a[2]); }
+
+static int cmp_i64(const void *a, const void *b) {
+  int64_t x = *(const int64_t *)a, y = *(const int64_t *)b;
+  return x < y ? -1 : x > y;
+}
+typedef struct { int64_t key[4]; int64_t cell; int face; } side_t;
+static int cmp_side(const void *a, const void *b) {
+  const side_t *x = a, *y = b;
+  for (int k = 0; k < 4; ++k) if (x->key[k] != y->key[k]) return x->key[k] < y->key[k] ? -1 : 1;
+  return x->cell < y->cell ? -1 : x->cell > y->cell;
+}
+
+/* fill the per-face caches for one side: fr/lobatto.hpp:72-163 by coordinate matching
+ * (polynomial/hexahedron.hpp:821-928) */
+static void match_side(const oracle_t *o, int64_t cell, int lf, const double *fxyz, int *node, int *dir,
+    double *scale) {
+  int q = o->q, n = o->n, fq = q * q;
+  int d = (lf == 2 || lf == 4) ? 0 : (lf == 1 || lf == 3) ? 1 : 2;
+  int plus = (lf == 2 || lf == 3 || lf == 5);
+  *dir = d;
+  for (int p = 0; p < fq; ++p) {
+    int found = -1;
+    for (int c = 0; c < n && found < 0; ++c) {
+      const double *y = &o->xyz[(cell * n + c) * 3];
+      double e[3] = {y[0] - fxyz[p * 3], y[1] - fxyz[p * 3 + 1], y[2] - fxyz[p * 3 + 2]};
+      int ijk[3] = {c / fq, (c / q) % q, c % q};
+      if (ijk[d] != (plus ? q - 1 : 0)) continue;
+      if (norm3(e) < 1e-8) found = c;
+    }
+    if (found < 0) abort();
+    node[p] = found;
+    const double *js = &o->jstar[(cell * n + found) * 9];
+    double nrm[3] = {js[0 * 3 + d], js[1 * 3 + d], js[2 * 3 + d]};
+    scale[p] = plus ? norm3(nrm) : -norm3(nrm);
+  }
+}
+
+void *oracle_create(int degree, int scheme, int riemann, int64_t n_nodes, const double *nodes,
+    int64_t n_cells, const int64_t *cn, int64_t n_bfaces, const int64_t *bf, const int32_t *btag) {
+  (void)n_nodes;
+  oracle_t *o = calloc(1, sizeof *o);
+  int q = degree + 1, n = q * q * q, fq = q * q;
+  o->degree = degree; o->q = q; o->n = n; o->scheme = scheme; o->riemann = riemann; o->n_cells = n_cells;
+  lobatto(q, o->x, o->w);
+  for (int i = 0; i < q; ++i) for (int m = 0; m < q; ++m) o->d1[i][m] = lagrange_d(q, o->x, m, i);
+  o->xyz = malloc(sizeof(double) * n_cells * n * 3);
+  o->jstar = malloc(sizeof(double) * n_cells * n * 9);
+  o->jinv = malloc(sizeof(double) * n_cells * n * 9);
+  o->det = malloc(sizeof(double) * n_cells * n);
+  o->length = malloc(sizeof(double) * n_cells);
+  for (int64_t c = 0; c < n_cells; ++c) {
+    double vol = 0;
+    for (int a = 0; a < n; ++a) {
+      int ijk[3] = {a / fq, (a / q) % q, a % q};
+      double loc[3] = {o->x[ijk[0]], o->x[ijk[1]], o->x[ijk[2]]};
+      double X[3] = {0, 0, 0}, J[3][3] = {{0}};
+      for (int v = 0; v < 8; ++v) { /* coordinate/hexahedron.hpp:413-456 */
+        const double *P = &nodes[cn[c * 8 + v] * 3];
+        double fx = 1 + VERT[v][0] * loc[0], fy = 1 + VERT[v][1] * loc[1], fz = 1 + VERT[v][2] * loc[2];
+        double shape = fx * fy * fz / 8;
+        double g[3] = {VERT[v][0] * (fy * fz / 8), VERT[v][1] * (fz * fx / 8), VERT[v][2] * (fx * fy / 8)};
+        for (int k = 0; k < 3; ++k) {
+          X[k] += shape * P[k];
+          for (int d = 0; d < 3; ++d) J[d][k] += g[d] * P[k]; /* J rows = local directions */
+        }
+      }
+      memcpy(&o->xyz[(c * n + a) * 3], X, sizeof X);
+      double c0[3], c1[3], c2[3];
+      cross(J[1], J[2], c0); cross(J[2], J[0], c1); cross(J[0], J[1], c2);
+      double det = J[0][0] * c0[0] + J[0][1] * c0[1] + J[0][2] * c0[2];
+      double *inv = &o->jinv[(c * n + a) * 9], *js = &o->jstar[(c * n + a) * 9];
+      for (int k = 0; k < 3; ++k) { /* inverse: columns are the cross products / det */
+        inv[k * 3 + 0] = c0[k] / det; inv[k * 3 + 1] = c1[k] / det; inv[k * 3 + 2] = c2[k] / det;
+      }
+      for (int k = 0; k < 9; ++k) js[k] = det * inv[k]; /* polynomial/hexahedron.hpp:228-230 */
+      o->det[c * n + a] = det;
+      vol += o->w[ijk[0]] * o->w[ijk[1]] * o->w[ijk[2]] * det; /* integrator/element.hpp:101-114 */
+    }
+    o->length[c] = cbrt(vol) * 0.5; /* mesh/part.hpp:230 */
+  }
+  /* faces from shared node sets (mesh/part.hpp:939-966, 1508-1531) */
+  side_t *sides = malloc(sizeof(side_t) * n_cells * 6);
+  for (int64_t c = 0; c < n_cells; ++c)
+    for (int f = 0; f < 6; ++f) {
+      side_t *s = &sides[c * 6 + f];
+      for (int m = 0; m < 4; ++m) s->key[m] = cn[c * 8 + FACE_NODES[f][m]];
+      qsort(s->key, 4, sizeof(int64_t), cmp_i64);
+      s->cell = c; s->face = f;
+    }
+  qsort(sides, n_cells * 6, sizeof(side_t), cmp_side);
+  int64_t max_faces = n_cells * 6;
+  o->holder = malloc(sizeof(int64_t) * max_faces); o->sharer = malloc(sizeof(int64_t) * max_faces);
+  o->tag = malloc(sizeof(int) * max_faces);
+  int *hface = malloc(sizeof(int) * max_faces), *sface = malloc(sizeof(int) * max_faces);
+  int64_t nf = 0;
+  for (int64_t i = 0; i + 1 < n_cells * 6; ++i)
+    if (memcmp(sides[i].key, sides[i + 1].key, sizeof sides[i].key) == 0) {
+      o->holder[nf] = sides[i].cell; hface[nf] = sides[i].face;       /* holder = smaller id */
+      o->sharer[nf] = sides[i + 1].cell; sface[nf] = sides[i + 1].face;
+      o->tag[nf] = -1; nf++; i++;
+    }
+  o->n_interior = nf;
+  for (int64_t b = 0; b < n_bfaces; ++b) {
+    side_t k;
+    for (int m = 0; m < 4; ++m) k.key[m] = bf[b * 4 + m];
+    qsort(k.key, 4, sizeof(int64_t), cmp_i64);
+    k.cell = -1;
+    int64_t lo = 0, hi = n_cells * 6;
+    while (lo < hi) { int64_t mid = (lo + hi) / 2; if (cmp_side(&sides[mid], &k) < 0) lo = mid + 1; else hi = mid; }
+    if (lo >= n_cells * 6 || memcmp(sides[lo].key, k.key, sizeof k.key) != 0) abort();
+    o->holder[nf] = sides[lo].cell; hface[nf] = sides[lo].face; o->sharer[nf] = -1; sface[nf] = -1;
+    o->tag[nf] = btag[b]; nf++;
+  }
+  o->n_faces = nf;
+  free(sides);
+  o->h_node = malloc(sizeof(int) * nf * fq); o->s_node = malloc(sizeof(int) * nf * fq);
+  o->h_dir = malloc(sizeof(int) * nf); o->s_dir = malloc(sizeof(int) * nf);
+  o->h_scale = malloc(sizeof(double) * nf * fq); o->s_scale = malloc(sizeof(double) * nf * fq);
+  o->frame = malloc(sizeof(frame_t) * nf * fq);
+  o->fweight = malloc(sizeof(double) * nf * fq);
+  o->fxyz = malloc(sizeof(double) * nf * fq * 3);
+  for (int64_t f = 0; f < nf; ++f) {
+    /* face quad in the holder's outward order (coordinate/cell.hpp:220-258) */
+    const double *P[4];
+    for (int m = 0; m < 4; ++m) P[m] = &nodes[cn[o->holder[f] * 8 + FACE_NODES[hface[f]][m]] * 3];
+    for (int ia = 0; ia < q; ++ia) for (int ib = 0; ib < q; ++ib) { /* integrator/quadrangle.hpp:66-79 */
+      int p = ia * q + ib;
+      double a = o->x[ia], b = o->x[ib], X[3] = {0, 0, 0}, Ja[3] = {0, 0, 0}, Jb[3] = {0, 0, 0};
+      for (int m = 0; m < 4; ++m) { /* coordinate/quadrangle.hpp:77-105 */
+        double fa = (1 + QUAD[m][0] * a), fb = (1 + QUAD[m][1] * b);
+        for (int k = 0; k < 3; ++k) {
+          X[k] += fa * fb / 4 * P[m][k];
+          Ja[k] += QUAD[m][0] * (fb / 4) * P[m][k];
+          Jb[k] += QUAD[m][1] * (fa / 4) * P[m][k];
+        }
+      }
+      memcpy(&o->fxyz[(f * fq + p) * 3], X, sizeof X);
+      frame_t *fr = &o->frame[f * fq + p]; /* coordinate/face.hpp:54-62 */
+      double nn[3]; cross(Ja, Jb, nn);
+      double len = norm3(nn), la = norm3(Ja);
+      for (int k = 0; k < 3; ++k) { fr->a[k] = nn[k] / len; fr->b[k] = Ja[k] / la; }
+      cross(fr->a, fr->b, fr->c);
+      /* sqrt(det(J J^T)), integrator/element.hpp:105-108 */
+      double aa = Ja[0] * Ja[0] + Ja[1] * Ja[1] + Ja[2] * Ja[2], bb = Jb[0] * Jb[0] + Jb[1] * Jb[1] + Jb[2] * Jb[2];
+      double ab = Ja[0] * Jb[0] + Ja[1] * Jb[1] + Ja[2] * Jb[2];
+      o->fweight[f * fq + p] = o->w[ia] * o->w[ib] * sqrt(aa * bb - ab * ab);
+    }
+    match_side(o, o->holder[f], hface[f], &o->fxyz[f * fq * 3], &o->h_node[f * fq], &o->h_dir[f], &o->h_scale[f * fq]);
+    if (o->sharer[f] >= 0)
+      match_side(o, o->sharer[f], sface[f], &o->fxyz[f * fq * 3], &o->s_node[f * fq], &o->s_dir[f], &o->s_scale[f * fq]);
+  }
+  free(hface); free(sface);
+  return o;
+}
+
+void oracle_destroy(void *h) {
+  oracle_t *o = h;
+  free(o->xyz); free(o->jstar); free(o->jinv); free(o->det); free(o->length); free(o->holder); free(o->sharer);
+  free(o->tag); free(o->h_node); free(o->s_node); free(o->h_dir); free(o->s_dir); free(o->h_scale);
+  free(o->s_scale); free(o->frame); free(o->fweight); free(o->fxyz); free(o);
+}
+
+void oracle_set_bc(void *h, int tag, int bc_kind, int field_kind, const double *prm) {
+  oracle_t *o = h;
+  o->bc_kind[tag] = bc_kind; o->field_kind[tag] = field_kind;
+  for (int k = 0; k < 8; ++k) o->field_prm[tag][k] = prm ? prm[k] : 0;
+}
+
+void oracle_approximate(void *h, int field_kind, const double *prm, double *column) { /* fem.hpp:147-154 */
+  oracle_t *o = h;
+  double p8[8] = {0};
+  for (int k = 0; k < 8 && prm; ++k) p8[k] = prm[k];
+  for (int64_t i = 0; i < o->n_cells * o->n; ++i) eval_field(field_kind, p8, &o->xyz[i * 3], 0.0, &column[i * 5]);
+}
+
+/* FiniteElement::GetResidualColumn (fem.hpp:248-258) with fr/general.hpp:249-288, fr/lobatto.hpp:232-428
+ * or dg/lobatto.hpp:143-302 */
+void oracle_residual(void *h, double t, const double *u, double *res) {
+  oracle_t *o = h;
+  int q = o->q, n = o->n, fq = q * q, K = 5;
+  int64_t nc = o->n_cells;
+  double *fhat = malloc(sizeof(double) * nc * n * 15); /* flux_matrices_ cache, fr/general.hpp:213-215 */
+  memset(res, 0, sizeof(double) * nc * n * K);
+  for (int64_t c = 0; c < nc; ++c) {
+    for (int a = 0; a < n; ++a) {
+      double F[5][3];
+      flux_matrix(&u[(c * n + a) * K], F);
+      const double *js = &o->jstar[(c * n + a) * 9];
+      double *fh = &fhat[(c * n + a) * 15];
+      for (int k = 0; k < 5; ++k) for (int d = 0; d < 3; ++d) /* hexahedron.hpp:607-611 */
+        fh[k * 3 + d] = F[k][0] * js[0 * 3 + d] + F[k][1] * js[1 * 3 + d] + F[k][2] * js[2 * 3 + d];
+    }
+    for (int a = 0; a < n; ++a) { /* dense over (a, b) like the reference; gradients are tensor products */
+      int ia[3] = {a / fq, (a / q) % q, a % q};
+      for (int b = 0; b < n; ++b) {
+        int ib[3] = {b / fq, (b / q) % q, b % q};
+        /* grad of basis b at node a: d/dxi_d = l_b'(x_a) in direction d when the other two indices agree */
+        double g[3];
+        g[0] = (ia[1] == ib[1] && ia[2] == ib[2]) ? o->d1[ia[0]][ib[0]] : 0;
+        g[1] = (ia[0] == ib[0] && ia[2] == ib[2]) ? o->d1[ia[1]][ib[1]] : 0;
+        g[2] = (ia[0] == ib[0] && ia[1] == ib[1]) ? o->d1[ia[2]][ib[2]] : 0;
+        if (g[0] == 0 && g[1] == 0 && g[2] == 0) continue;
+        if (o->scheme == 0) { /* fr/general.hpp:280-286: res[a] -= Fhat_b . grad phi_b(xi_a) */
+          const double *fh = &fhat[(c * n + b) * 15];
+          for (int k = 0; k < 5; ++k)
+            res[(c * n + a) * K + k] -= fh[k * 3] * g[0] + fh[k * 3 + 1] * g[1] + fh[k * 3 + 2] * g[2];
+        } else { /* dg/lobatto.hpp:161-170: res[b] += w_a det_a F_a . (J_a^-1 grad_local phi_b(xi_a)) */
+          double F[5][3];
+          flux_matrix(&u[(c * n + a) * K], F);
+          const double *inv = &o->jinv[(c * n + a) * 9];
+          double wa = o->w[ia[0]] * o->w[ia[1]] * o->w[ia[2]] * o->det[c * n + a];
+          double gg[3];
+          for (int x = 0; x < 3; ++x) gg[x] = inv[x * 3] * g[0] + inv[x * 3 + 1] * g[1] + inv[x * 3 + 2] * g[2];
+          for (int k = 0; k < 5; ++k)
+            res[(c * n + b) * K + k] += wa * (F[k][0] * gg[0] + F[k][1] * gg[1] + F[k][2] * gg[2]);
+        }
+      }
+    }
+  }
+  double gp = g_prime_right_at_one(o->degree);
+  for (int64_t f = 0; f < o->n_faces; ++f) {
+    int64_t ch = o->holder[f], cs = o->sharer[f];
+    for (int p = 0; p < fq; ++p) {
+      const frame_t *fr = &o->frame[f * fq + p];
+      int ah = o->h_node[f * fq + p];
+      const double *uh = &u[(ch * n + ah) * K];
+      double fu[5];
+      if (cs >= 0) {
+        int as = o->s_node[f * fq + p];
+        flux_upwind(o->riemann, fr, uh, &u[(cs * n + as) * K], fu);
+        if (o->scheme == 0) { /* fr/general.hpp:296-315, fr/lobatto.hpp:232-251 */
+          double sh = o->h_scale[f * fq + p], ss = o->s_scale[f * fq + p];
+          double gh = sh > 0 ? gp : -gp, gs = ss > 0 ? gp : -gp;
+          const double *Fh = &fhat[(ch * n + ah) * 15], *Fs = &fhat[(cs * n + as) * 15];
+          for (int k = 0; k < 5; ++k) {
+            double f_holder = fu[k] * sh - Fh[k * 3 + o->h_dir[f]];
+            double f_sharer = fu[k] * (-ss) - Fs[k * 3 + o->s_dir[f]];
+            res[(ch * n + ah) * K + k] -= f_holder * gh;
+            res[(cs * n + as) * K + k] -= f_sharer * gs;
+          }
+        } else { /* dg/lobatto.hpp:171-191 */
+          double wf = o->fweight[f * fq + p];
+          for (int k = 0; k < 5; ++k) {
+            res[(ch * n + ah) * K + k] -= fu[k] * wf;
+            res[(cs * n + as) * K + k] += fu[k] * wf;
+          }
+        }
+      } else {
+        int tag = o->tag[f], kind = o->bc_kind[tag];
+        double given[5] = {0, 0, 0, 0, 0};
+        if (kind >= 2) eval_field(o->field_kind[tag], o->field_prm[tag], &o->fxyz[(f * fq + p) * 3], t, given);
+        boundary_flux(o->riemann, kind, fr, uh, given, fu);
+        if (o->scheme == 0) { /* fr/lobatto.hpp:278-428 */
+          double sh = o->h_scale[f * fq + p], gh = sh > 0 ? gp : -gp;
+          const double *Fh = &fhat[(ch * n + ah) * 15];
+          for (int k = 0; k < 5; ++k) res[(ch * n + ah) * K + k] -= (fu[k] * sh - Fh[k * 3 + o->h_dir[f]]) * gh;
+        } else { /* dg/lobatto.hpp:192-302 */
+          double wf = o->fweight[f * fq + p];
+          for (int k = 0; k < 5; ++k) res[(ch * n + ah) * K + k] -= fu[k] * wf;
+        }
+      }
+    }
+  }
+  for (int64_t c = 0; c < nc; ++c)
+    for (int a = 0; a < n; ++a) {
+      int ia[3] = {a / fq, (a / q) % q, a % q};
+      double s = o->scheme == 0 ? 1.0 / o->det[c * n + a] /* fr/general.hpp:256-266 */
+          : 1.0 / (o->w[ia[0]] * o->w[ia[1]] * o->w[ia[2]] * o->det[c * n + a]); /* dg/lobatto.hpp:143-158 */
+      for (int k = 0; k < 5; ++k) res[(c * n + a) * K + k] *= s;
+    }
+  free(fhat);
+}
+
+/* temporal/rk.hpp:16-49 with temporal/ode.hpp:121-133, on whole columns */
+void oracle_rk_update(void *h, int order, double t, double dt, double *u) {
+  oracle_t *o = h;
+  int64_t m = o->n_cells * o->n * 5;
+  double *r = malloc(sizeof(double) * m), *u0 = malloc(sizeof(double) * m), *un = malloc(sizeof(double) * m);
+  memcpy(u0, u, sizeof(double) * m);
+#define EULER_NEXT(tt, dst) do { oracle_residual(o, (tt), u, r); \
+    for (int64_t i = 0; i < m; ++i) { r[i] *= dt; dst[i] = u[i] + r[i]; } } while (0)
+  if (order == 1) {
+    EULER_NEXT(t, un); memcpy(u, un, sizeof(double) * m);
+  } else if (order == 2) {
+    EULER_NEXT(t, un); memcpy(u, un, sizeof(double) * m);
+    EULER_NEXT(t + dt, un);
+    for (int64_t i = 0; i < m; ++i) { un[i] += u0[i]; un[i] *= 0.5; u[i] = un[i]; }
+  } else {
+    EULER_NEXT(t, un); memcpy(u, un, sizeof(double) * m);
+    EULER_NEXT(t + dt, un);
+    for (int64_t i = 0; i < m; ++i) { double v = u0[i] * 3; v += un[i]; v /= 4; u[i] = v; }
+    EULER_NEXT(t + dt / 2, un);
+    for (int64_t i = 0; i < m; ++i) { double v = un[i] * 2; v += u0[i]; v /= 3; u[i] = v; }
+  }
+#undef EULER_NEXT
+  free(r); free(u0); free(un);
+}
+
+/* fem.hpp:26-37, 411-435; fr/lobatto.hpp:220-222; rotated/euler.hpp:340-345 */
+double oracle_time_step(void *h, const double *u, double dt_guess, int rk_order) {
+  static const double cfl[5][9] = {
+    {1.000}, {1.000, 0.333}, {1.000, 0.333, 0.209, 0.130, 0.089, 0.066, 0.051, 0.040, 0.033},
+    {1.256, 0.409, 0.209, 0.130, 0.089, 0.066, 0.051, 0.040, 0.033},
+    {1.392, 0.464, 0.235, 0.145, 0.100, 0.073, 0.056, 0.045, 0.037}};
+  oracle_t *o = h;
+  double min_dt = 1e100;
+  for (int64_t c = 0; c < o->n_cells; ++c) {
+    double vmax = 1e-5;
+    for (int a = 0; a < o->n; ++a) {
+      prim_t q = cons_to_prim(&u[(c * o->n + a) * 5]);
+      double cs = sound_speed(q.rho, q.p), v = sqrt(q.u * q.u + q.v * q.v + q.w * q.w);
+      double s = cs + v > cs - v ? cs + v : cs - v;
+      if (s > vmax) vmax = s;
+    }
+    double d = o->length[c] / vmax;
+    if (d < min_dt) min_dt = d;
+  }
+  double dt = cfl[rk_order][o->degree] * min_dt;
+  if (dt_guess < dt) dt = dt_guess;
+  if (o->scheme == 0) { dt *= 2.0; if (dt_guess < dt) dt = dt_guess; }
+  return dt;
+}
+
+/* one rotated Riemann problem (test hook) */
+void oracle_riemann_flux(int riemann, int bc_kind, const double *frame9, const double *ul, const double *ur,
+    double *f) {
+  frame_t fr;
+  memcpy(fr.a, frame9, sizeof fr.a); memcpy(fr.b, frame9 + 3, sizeof fr.b); memcpy(fr.c, frame9 + 6, sizeof fr.c);
+  if (bc_kind < 0) flux_upwind(riemann, &fr, ul, ur, f);
+  else boundary_flux(riemann, bc_kind, &fr, ul, ur, f);
+}
+/* 1-D solver on primitive states (rho, u, v, w, p), for the Toro known-answer tests */
+void oracle_riemann_1d(int riemann, const double *pl, const double *pr, double *f) {
+  prim_t l = {pl[0], pl[1], pl[2], pl[3], pl[4]}, r = {pr[0], pr[1], pr[2], pr[3], pr[4]};
+  solve_1d(riemann, &l, &r, f);
+}

@@ -1,0 +1,77 @@
+"""Shared parity cases: meshes, boundary set-ups and fields used by the golden generator, the oracle
+pinning tests, the host-logic tests and the GPU parity tests."""
+from __future__ import annotations
+
+import numpy as np
+
+from minicfd_b200 import fields, mesh
+
+# bc kinds (same numbering in refapi, oracle_check and capi)
+WALL, SUP_OUT, SUP_IN, SUB_IN, SUB_OUT, SMART = range(6)
+
+MIXED_BCS = {0: WALL, 1: SUP_OUT, 2: SUP_IN, 3: SMART, 4: SUB_OUT, 5: SUB_IN}
+SUBSONIC_INLET_STATE = [2.0, 0.0, 0.0, -1.0, 0.01]   # p_total, direction cosines (into zmax), T_total
+SMOOTH_A = 1.3
+
+
+def small_mesh(seed=3):
+    """3x3x2 warped box with every cell randomly rotated and the cell order permuted."""
+    return mesh.scramble(mesh.box(3, 3, 2, warp=0.15, seed=seed), seed=seed)
+
+
+def noisy_state(pts, seed=0, amp=1e-3):
+    """Smooth admissible field + multiplicative noise, so that neighbouring cells never hold identical
+    face states (the Exact solver's Newton start is a sign test on f(p_left), which is rounding noise
+    for identical states: exact.hpp:140-152)."""
+    u = fields.smooth(1.0)(pts, 0.0)
+    rng = np.random.default_rng(seed)
+    return (u * (1 + amp * rng.uniform(-1, 1, size=u.shape))).reshape(-1)
+
+
+def apply_bcs_ref(r, kinds=MIXED_BCS):
+    import refapi
+    for tag, k in kinds.items():
+        if k == SUB_IN:
+            r.set_bc(tag, k, refapi.F_CONST, SUBSONIC_INLET_STATE)
+        else:
+            r.set_bc(tag, k, refapi.F_SMOOTH, [SMOOTH_A])
+
+
+def apply_bcs_oracle(o, kinds=MIXED_BCS):
+    import oracle_check as oc
+    for tag, k in kinds.items():
+        if k == SUB_IN:
+            o.set_bc(tag, k, oc.F_CONST, SUBSONIC_INLET_STATE)
+        else:
+            o.set_bc(tag, k, oc.F_SMOOTH, [SMOOTH_A])
+
+
+def bc_function(kind):
+    if kind == SUB_IN:
+        return fields.constant(SUBSONIC_INLET_STATE)
+    return fields.smooth(SMOOTH_A)
+
+
+def apply_bcs_spatial(sp, kinds=MIXED_BCS):
+    for tag, k in kinds.items():
+        f = bc_function(k)
+        if k == WALL:
+            sp.SetInviscidWall(tag)
+        elif k == SUP_OUT:
+            sp.SetSupersonicOutlet(tag)
+        elif k == SUP_IN:
+            sp.SetSupersonicInlet(tag, f)
+        elif k == SUB_IN:
+            sp.SetSubsonicInlet(tag, f)
+        elif k == SUB_OUT:
+            sp.SetSubsonicOutlet(tag, f)
+        else:
+            sp.SetSmartBoundary(tag, f)
+
+
+GOLDEN_CASES = [  # (name, degree, scheme, riemann)
+    ("fr_p2_exact", 2, 0, 0), ("fr_p2_hllc", 2, 0, 1), ("fr_p2_ausm", 2, 0, 2),
+    ("dg_p2_hllc", 2, 1, 1), ("fr_p3_hllc", 3, 0, 1), ("dg_p3_ausm", 3, 1, 2),
+]
+GOLDEN_T = 0.25
+GOLDEN_DT = 1e-3

@@ -1,0 +1,39 @@
+"""Generates tests/golden/*.npz from the UNMODIFIED reference (oracle/_ref, built from /root/reference
+by `make -C oracle ref`).  Run in the build container only: `python tests/golden/make_golden.py`.
+
+Each file holds, for one (degree, scheme, Riemann solver): the input column, the reference's residual
+at t = GOLDEN_T with the mixed boundary set-up of tests/cases.py, its time step, and the state after
+one RungeKutta<3>::Update from t = 0 — all on tests/cases.small_mesh().
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+
+import cases  # noqa: E402
+import refapi  # noqa: E402
+from minicfd_b200.part import cell_points  # noqa: E402
+
+
+def main():
+    m = cases.small_mesh()
+    for name, degree, scheme, riemann in cases.GOLDEN_CASES:
+        r = refapi.Ref(m, degree=degree, scheme=scheme, riemann=riemann)
+        cases.apply_bcs_ref(r)
+        u = cases.noisy_state(cell_points(m.nodes, m.cells, degree))
+        r.set_solution(u)
+        res = r.residual(cases.GOLDEN_T)
+        dt = r.time_step(1.0, 3)
+        r.rk_update(3, 0.0, cases.GOLDEN_DT, 1)
+        u_rk3 = r.get_solution()
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), u=u, residual=res, dt=dt, u_rk3=u_rk3,
+                            nodes=m.nodes, cells=m.cells, bfaces=m.bfaces, btags=m.btags)
+        print(name, np.linalg.norm(res), dt)
+
+
+if __name__ == "__main__":
+    main()

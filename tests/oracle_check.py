@@ -1,0 +1,120 @@
+"""ctypes access to oracle/libminicfd_oracle.so (the plain-C restatement; TEST INFRASTRUCTURE) plus
+helpers that pick the strongest checker available: the reference itself (oracle/_ref) when it was
+built, else the C restatement."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB = os.path.join(ROOT, "oracle", "libminicfd_oracle.so")
+_lib = None
+
+F_CONST, F_VORTEX, F_SMOOTH = 0, 1, 3
+
+
+def available():
+    return os.path.exists(LIB)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = C.CDLL(LIB)
+        _lib.oracle_create.restype = C.c_void_p
+        _lib.oracle_time_step.restype = C.c_double
+    return _lib
+
+
+def _dp(a):
+    return None if a is None else a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+class Oracle:
+    def __init__(self, mesh, degree=2, scheme=0, riemann=1):
+        nodes = np.ascontiguousarray(mesh.nodes, dtype=np.float64)
+        cells = np.ascontiguousarray(mesh.cells, dtype=np.int64)
+        bf = np.ascontiguousarray(mesh.bfaces, dtype=np.int64)
+        bt = np.ascontiguousarray(mesh.btags, dtype=np.int32)
+        self.n_cells = len(cells)
+        self.kfields = 5 * (degree + 1) ** 3
+        self.h = C.c_void_p(lib().oracle_create(
+            C.c_int(degree), C.c_int(scheme), C.c_int(riemann), C.c_int64(len(nodes)), _dp(nodes),
+            C.c_int64(len(cells)), cells.ctypes.data_as(C.POINTER(C.c_int64)), C.c_int64(len(bf)),
+            bf.ctypes.data_as(C.POINTER(C.c_int64)), bt.ctypes.data_as(C.POINTER(C.c_int32))))
+
+    def __del__(self):
+        try:
+            if self.h:
+                lib().oracle_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def set_bc(self, tag, bc_kind, field_kind=F_CONST, params=None):
+        p = np.zeros(8)
+        if params is not None:
+            p[:len(params)] = params
+        lib().oracle_set_bc(self.h, C.c_int(tag), C.c_int(bc_kind), C.c_int(field_kind), _dp(p))
+
+    def approximate(self, field_kind, params=None):
+        p = np.zeros(8)
+        if params is not None:
+            p[:len(params)] = params
+        out = np.empty(self.n_cells * self.kfields)
+        lib().oracle_approximate(self.h, C.c_int(field_kind), _dp(p), _dp(out))
+        return out
+
+    def residual(self, u, t=0.0):
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        out = np.empty_like(u)
+        lib().oracle_residual(self.h, C.c_double(t), _dp(u), _dp(out))
+        return out
+
+    def rk_update(self, u, order, t, dt):
+        u = np.array(u, dtype=np.float64, copy=True)
+        lib().oracle_rk_update(self.h, C.c_int(order), C.c_double(t), C.c_double(dt), _dp(u))
+        return u
+
+    def time_step(self, u, dt_guess, rk_order):
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        return float(lib().oracle_time_step(self.h, _dp(u), C.c_double(dt_guess), C.c_int(rk_order)))
+
+
+def riemann_flux(kind, frame, ul, ur, bc=-1):
+    out = np.empty(5)
+    fr = np.ascontiguousarray(frame, dtype=np.float64)
+    ul = np.ascontiguousarray(ul, dtype=np.float64); ur = np.ascontiguousarray(ur, dtype=np.float64)
+    lib().oracle_riemann_flux(C.c_int(kind), C.c_int(bc), _dp(fr), _dp(ul), _dp(ur), _dp(out))
+    return out
+
+
+def riemann_1d(kind, pl, pr):
+    out = np.empty(5)
+    pl = np.ascontiguousarray(pl, dtype=np.float64); pr = np.ascontiguousarray(pr, dtype=np.float64)
+    lib().oracle_riemann_1d(C.c_int(kind), _dp(pl), _dp(pr), _dp(out))
+    return out
+
+
+def which():
+    import refapi
+    return "reference (oracle/_ref)" if refapi.available(2) else "C restatement (oracle/minicfd_oracle.c)"
+
+
+def residual_and_rk3(mesh, u0, *, degree, scheme, riemann, dt, walls=True):
+    """Residual at t=0 and the state after one RK3 step, all boundaries inviscid walls."""
+    import refapi
+    if refapi.available(degree):
+        r = refapi.Ref(mesh, degree=degree, scheme=scheme, riemann=riemann)
+        for tag in range(6):
+            r.set_bc(tag, refapi.WALL)
+        r.set_solution(u0)
+        res = r.residual(0.0)
+        r.rk_update(3, 0.0, dt, 1)
+        return res, r.get_solution()
+    o = Oracle(mesh, degree, scheme, riemann)
+    for tag in range(6):
+        o.set_bc(tag, 0)
+    return o.residual(u0, 0.0), o.rk_update(u0, 3, 0.0, dt)

@@ -1,0 +1,179 @@
+"""CPU-only tests of everything around the kernels: the C-ABI library loads and exports what the
+header declares, the Part bookkeeping matches the reference's numbering rules, the kernel *source*
+(compiled for the host, tests/host_emulation) reproduces the oracle, and the halo exchange logic
+works across two gloo ranks."""
+import ctypes
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import cases
+import emuapi
+import oracle_check as oc
+import refapi
+from minicfd_b200 import capi, fields, mesh as meshmod
+from minicfd_b200.part import Part, cell_points, dual_graph
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def relerr(a, b):
+    return np.abs(a - b).max() / np.abs(b).max()
+
+
+def test_library_exports_every_declared_symbol():
+    """The C ABI loads without a GPU and exports each function of include/minicfd_b200.h."""
+    header = open(os.path.join(ROOT, "include", "minicfd_b200.h")).read()
+    declared = set(re.findall(r"\b(mcfd_[a-z_0-9]+)\s*\(", header)) - {"mcfd_time_callback"}
+    assert declared == set(capi.SYMBOLS), declared ^ set(capi.SYMBOLS)
+    lib = ctypes.CDLL(capi.LIB_PATH)
+    for name in declared:
+        assert hasattr(lib, name), name
+
+
+def test_no_cpu_fallback_without_gpu():
+    """Without a device mcfd_create must fail loudly (no fallback); with one it must succeed."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(capi.McfdError, match="no CUDA device|CUDA"):
+        capi.Context()
+
+
+def test_product_never_touches_the_checkers():
+    """Nothing under minicfd_b200/ or include/ may import or link oracle/ or tests/ code."""
+    bad = re.compile(r"(import|from)\s+(oracle|refapi|emuapi|oracle_check|cases)\b|libminicfd_ref|"
+                     r"libminicfd_oracle|libmcfd_emu|#include\s+\"[^\"]*(oracle|tests)/|dlopen")
+    for base in ("minicfd_b200", "include"):
+        for dirpath, _, files in os.walk(os.path.join(ROOT, base)):
+            for f in files:
+                if f.endswith((".py", ".cu", ".cuh", ".hpp", ".h", ".cpp")):
+                    text = open(os.path.join(dirpath, f)).read()
+                    assert not bad.search(text), (f, bad.search(text).group(0))
+
+
+@pytest.mark.skipif(not refapi.available(2), reason="oracle/_ref not built")
+def test_part_numbering_matches_reference_rules():
+    m = meshmod.scramble(meshmod.box(4, 3, 3, warp=0.1), seed=1)
+    parts = np.random.default_rng(0).integers(0, 3, size=m.n_cells).astype(np.int32)
+    r = refapi.Ref(m, degree=2, cell_parts=parts, n_parts=3)
+    pairs = dual_graph(m)
+    for rank in range(3):
+        p = Part(m, parts, rank, 3, pairs=pairs)
+        assert np.array_equal(r.cell_global_ids(rank), p.global_ids)      # inner, inter, then ghosts
+        assert r.count_local(rank) == p.n_local and r.count_ghost(rank) == p.n_ghost
+        sp, sc, scell = r.halo(rank, 1)
+        rp, rc, rcell = r.halo(rank, 0)
+        assert np.array_equal(sp, p.neighbours) and np.array_equal(rp, p.neighbours)
+        assert np.array_equal(scell, np.concatenate(p.send_cells))
+        assert np.array_equal(rcell, np.concatenate(p.recv_cells))
+
+
+def test_block_partition_and_periodic_graph():
+    m = meshmod.box(4, 4, 2)
+    parts = meshmod.block_partition(m, 2, 2, 1)
+    assert sorted(np.bincount(parts)) == [8, 8, 8, 8]
+    assert len(dual_graph(meshmod.box(3, 3, 3, periodic=True))) == 81
+    assert len(dual_graph(meshmod.box(3, 3, 3))) == 54
+
+
+@pytest.mark.parametrize("name,degree,scheme,riemann", cases.GOLDEN_CASES)
+def test_kernel_source_on_host_matches_golden(name, degree, scheme, riemann):
+    """The device code of the stage kernel, run thread by thread on the host, against the reference's
+    golden residual and RK3 state (mixed boundary kinds, scrambled warped mesh)."""
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    m = meshmod.HexMesh(nodes=g["nodes"], cells=g["cells"], bfaces=g["bfaces"], btags=g["btags"])
+    holder, hf, tags, pts = emuapi.boundary(m, degree)
+    def bvals(t):
+        out = np.zeros(pts.shape[:2] + (5,))
+        for tag, kind in cases.MIXED_BCS.items():
+            sel = tags == tag
+            out[sel] = cases.bc_function(kind)(pts[sel], t)
+        return out
+    u = g["u"]
+    res = emuapi.stage(m, degree, scheme, riemann, u, tag_kinds=cases.MIXED_BCS, bvals=bvals(cases.GOLDEN_T))
+    assert relerr(res, g["residual"]) < 1e-12
+    dt = cases.GOLDEN_DT
+    kw = dict(tag_kinds=cases.MIXED_BCS, dt=dt)
+    u1 = emuapi.stage(m, degree, scheme, riemann, u, bvals=bvals(0.0), mode=1, **kw)
+    u2 = emuapi.stage(m, degree, scheme, riemann, u1, bvals=bvals(dt), column_u0=u, mode=2, **kw)
+    u3 = emuapi.stage(m, degree, scheme, riemann, u2, bvals=bvals(dt / 2), column_u0=u, mode=3, **kw)
+    assert relerr(u3, g["u_rk3"]) < 1e-12
+
+
+def test_kernel_source_periodic_equals_embedded_box():
+    """A periodic box must give the same residuals as the interior of a larger box fed with the same
+    2*pi-periodic field (GPU-only periodic variant of BASELINE config 2)."""
+    L = 2 * np.pi
+    m = meshmod.box(4, 4, 4, hi=(L, L, L), periodic=True)
+    u = fields.smooth(1.0)(cell_points(m.nodes, m.cells, 2), 0.0).reshape(-1)
+    res = emuapi.stage(m, 2, 0, 1, u)
+    h = L / 4
+    mb = meshmod.box(6, 6, 6, lo=(-h,) * 3, hi=(L + h,) * 3)
+    ub = fields.smooth(1.0)(cell_points(mb.nodes, mb.cells, 2), 0.0).reshape(-1)
+    resb = emuapi.stage(mb, 2, 0, 1, ub).reshape(6, 6, 6, 135)
+    assert relerr(res, resb[1:5, 1:5, 1:5].reshape(-1)) < 1e-12
+
+
+def test_kernel_source_with_ghost_cells_matches_single_part():
+    """A part with ghost cells (fed with the neighbours' coefficients) reproduces the single-part
+    residual on its local cells: the ghost-face path of fem.hpp:374-380."""
+    m = cases.small_mesh(seed=9)
+    parts = (np.arange(m.n_cells) % 2).astype(np.int32)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, 2))
+    o = oc.Oracle(m, 2, 0, 1)
+    for tag in range(6):
+        o.set_bc(tag, 0)
+    full = o.residual(u, 0.0).reshape(-1, 135)
+    for rank in range(2):
+        p = Part(m, parts, rank, 2)
+        col = u.reshape(-1, 135)[p.global_ids].reshape(-1)
+        class Sub:  # the part's own view of the mesh
+            nodes, periodic = m.nodes, None
+        res = emuapi.stage(Sub, 2, 0, 1, col, n_local=p.n_local, n_ghost=p.n_ghost, cells=p.cell_nodes,
+                           bfaces=p.bfaces, btags=p.btags)
+        assert relerr(res.reshape(-1, 135), full[p.local_global]) < 1e-12
+
+
+_GLOO_WORKER = r'''
+import os, sys
+sys.path.insert(0, sys.argv[1])
+import numpy as np, torch, torch.distributed as dist
+from minicfd_b200 import mesh as meshmod, halo
+from minicfd_b200.part import Part
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+dist.init_process_group("gloo", rank=rank, world_size=world)
+m = meshmod.scramble(meshmod.box(4, 3, 2, warp=0.1), seed=2)
+parts = (np.arange(m.n_cells) * world // m.n_cells).astype(np.int32)
+p = Part(m, parts, rank, world)
+K = 7
+field = np.arange(m.n_cells * K, dtype=np.float64).reshape(m.n_cells, K) * 1.5   # global "coefficients"
+ex = halo.for_part(p, K)
+send = torch.from_numpy(field[p.global_ids[np.concatenate(p.send_cells)]].reshape(-1).copy())
+recv = torch.zeros(int(sum(len(c) for c in p.recv_cells)) * K, dtype=torch.float64)
+ex.bind(send, recv)
+ex.exchange()
+expect = field[p.global_ids[np.concatenate(p.recv_cells)]].reshape(-1)
+assert np.array_equal(recv.numpy(), expect), "ghost data mismatch"
+dt = ex.allreduce_min(1.0 + rank)
+assert dt == 1.0
+dist.destroy_process_group()
+print("OK", rank)
+'''
+
+
+def test_halo_exchange_two_gloo_ranks(tmp_path):
+    """world_size-2 gloo run of the exchange used for N > 1 GPUs (pack order = send_cell_ptrs_, unpack
+    order = recv_cell_ptrs_; part.hpp:1242-1314) and of the dt all-reduce."""
+    script = tmp_path / "worker.py"
+    script.write_text(_GLOO_WORKER)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", "29541", str(script), ROOT]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert out.stdout.count("OK") == 2

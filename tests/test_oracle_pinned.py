@@ -1,0 +1,134 @@
+"""Pins the CPU checkers: the plain-C restatement (oracle/minicfd_oracle.c) against (1) the golden
+vectors generated from the unmodified reference, (2) the reference itself when oracle/_ref was built
+here, and (3) the known-answer Riemann states the reference's own tests use.  CPU only."""
+import os
+
+import numpy as np
+import pytest
+
+import cases
+import oracle_check as oc
+import refapi
+from minicfd_b200 import mesh as meshmod
+from minicfd_b200.part import cell_points
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+TOL = 1e-12
+
+
+def _golden_mesh(g):
+    return meshmod.HexMesh(nodes=g["nodes"], cells=g["cells"], bfaces=g["bfaces"], btags=g["btags"])
+
+
+def relerr(a, b):
+    return np.abs(a - b).max() / np.abs(b).max()
+
+
+@pytest.mark.parametrize("name,degree,scheme,riemann", cases.GOLDEN_CASES)
+def test_c_oracle_matches_golden(name, degree, scheme, riemann):
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    o = oc.Oracle(_golden_mesh(g), degree, scheme, riemann)
+    cases.apply_bcs_oracle(o)
+    assert relerr(o.residual(g["u"], cases.GOLDEN_T), g["residual"]) < TOL
+    assert o.time_step(g["u"], 1.0, 3) == pytest.approx(float(g["dt"]), rel=1e-14)
+    assert relerr(o.rk_update(g["u"], 3, 0.0, cases.GOLDEN_DT), g["u_rk3"]) < TOL
+
+
+def test_golden_mesh_is_the_generated_mesh():
+    g = np.load(os.path.join(GOLDEN, "fr_p2_hllc.npz"))
+    m = cases.small_mesh()
+    assert np.array_equal(m.cells, g["cells"]) and np.array_equal(m.nodes, g["nodes"])
+    assert np.array_equal(cases.noisy_state(cell_points(m.nodes, m.cells, 2)), g["u"])
+
+
+@pytest.mark.skipif(not refapi.available(2), reason="oracle/_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("degree", [2, 3])
+@pytest.mark.parametrize("scheme", [0, 1])
+@pytest.mark.parametrize("riemann", [0, 1, 2])
+def test_c_oracle_matches_reference(degree, scheme, riemann):
+    m = meshmod.scramble(meshmod.box(3, 2, 2, warp=0.2, seed=11), seed=5)
+    r = refapi.Ref(m, degree=degree, scheme=scheme, riemann=riemann)
+    o = oc.Oracle(m, degree, scheme, riemann)
+    cases.apply_bcs_ref(r)
+    cases.apply_bcs_oracle(o)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), seed=7)
+    r.set_solution(u)
+    assert relerr(o.residual(u, 0.1), r.residual(0.1)) < TOL
+    assert o.time_step(u, 1.0, 3) == r.time_step(1.0, 3)
+    for order in (1, 2, 3):
+        r.set_solution(u)
+        r.rk_update(order, 0.0, 2e-3, 1)
+        assert relerr(o.rk_update(u, order, 0.0, 2e-3), r.get_solution()) < TOL
+
+
+def _flux_1d(rho, u, p):
+    """Flux of a 1-D primitive state (test/riemann/euler/exact.cpp:34-39)."""
+    e = p / 0.4 + 0.5 * rho * u * u
+    return np.array([rho * u, rho * u * u + p, (e + p) * u])
+
+
+# (left, right, state on the t-axis) from test/riemann/euler/exact.cpp:57-85 (Toro's tables), 1e-4 rel.
+TORO = [
+    ((1.0, 0.0, 1.0), (0.125, 0.0, 0.1), (0.426319, +0.927453, 0.303130)),
+    ((0.125, 0.0, 0.1), (1.0, 0.0, 1.0), (0.426319, -0.927453, 0.303130)),
+    ((5.99924, 19.5975, 460.894), (5.99242, 6.19633, 46.0950), (5.99924, 19.5975, 460.894)),
+    ((1.0, 0.0, 1000), (1.0, 0.0, 0.01), (0.575062, 19.59745, 460.8938)),
+    ((1.0, 0.0, 0.01), (1.0, 0.0, 100), (0.575113, -6.196328, 46.09504)),
+    ((1.0, -2.0, 0.4), (1.0, +2.0, 0.4), (0.21852, 0.0, 0.001894)),
+]
+
+
+@pytest.mark.parametrize("left,right,axis", TORO)
+def test_exact_riemann_known_answers(left, right, axis):
+    f = oc.riemann_1d(0, [left[0], left[1], 0, 0, left[2]], [right[0], right[1], 0, 0, right[2]])
+    expect = _flux_1d(*axis)
+    got = np.array([f[0], f[1], f[4]])
+    for g, e in zip(got, expect):
+        if e == 0:
+            assert abs(g) < 1e-4   # the reference compares a rounded table value
+        else:
+            assert g / e == pytest.approx(1.0, abs=1e-4)
+
+
+def test_exact_riemann_vacuum():
+    """test/riemann/euler/exact.cpp:86-89: both expansions run into vacuum -> zero flux."""
+    f = oc.riemann_1d(0, [1.0, -4.0, 0, 0, 0.4], [1.0, +4.0, 0, 0, 0.4])
+    assert np.all(f == 0)
+
+
+def test_right_vacuum_inside_expansion():
+    """test/riemann/euler/exact.cpp:90-138 (a_L = 1, u_L = -4: the t-axis lies inside wave 1)."""
+    f = oc.riemann_1d(0, [1.4, -4.0, 0, 0, 1.0], [0, 100.0, 0, 0, 0])
+    expect = _flux_1d(1.4 * 6.0 ** -5, 6.0 ** -1, 6.0 ** -7)
+    assert abs(f[0] - expect[0]) < 1e-19 and abs(f[1] - expect[1]) < 1e-19 and abs(f[4] - expect[2]) < 1e-20
+
+
+@pytest.mark.parametrize("kind", [1, 2])
+def test_upwind_consistency(kind):
+    """hllc.cpp / ausm.cpp of the reference: equal states give the physical flux."""
+    f = oc.riemann_1d(kind, [1.0, 0.3, 0.1, -0.2, 1.0], [1.0, 0.3, 0.1, -0.2, 1.0])
+    ke = 0.5 * (0.09 + 0.01 + 0.04)
+    e = 1.0 / 0.4 + ke
+    assert f == pytest.approx([0.3, 0.09 + 1.0, 0.03, -0.06, (e + 1.0) * 0.3], rel=1e-14)
+
+
+@pytest.mark.skipif(not refapi.available(2), reason="oracle/_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("kind", [0, 1, 2])
+def test_rotated_riemann_matches_reference(kind):
+    """Random rotated problems incl. strong jumps, as in test/riemann/rotated/euler.cpp:80-148."""
+    rng = np.random.default_rng(31415926)
+    r = refapi.Ref(meshmod.box(1, 1, 1), degree=2)
+    for _ in range(300):
+        n = rng.normal(size=3); n /= np.linalg.norm(n)
+        t1 = np.cross(n, rng.normal(size=3)); t1 /= np.linalg.norm(t1)
+        frame = np.array([n, t1, np.cross(n, t1)])
+        def state():
+            rho, p = rng.uniform(0.1, 2.0), rng.uniform(0.1, 2.0)
+            v = rng.uniform(-1.5, 1.5, size=3)
+            return np.array([rho, *(rho * v), p / 0.4 + 0.5 * rho * v @ v])
+        ul, ur = state(), state()
+        a = r.riemann_flux(kind, frame, ul, ur)
+        b = oc.riemann_flux(kind, frame, ul, ur)
+        assert np.abs(a - b).max() <= 1e-12 * max(1.0, np.abs(a).max())
+        w = oc.riemann_flux(kind, frame, ul, ur, bc=0)
+        assert np.abs(w - r.riemann_flux(kind, frame, ul, ur, bc=0)).max() < 1e-14
