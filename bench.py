@@ -1,0 +1,334 @@
+#!/usr/bin/env python
+"""bench.py — BASELINE.json's metric on BASELINE.json's config.
+
+Metric: DOF-updates/s per RK stage (p=2 Euler, hexa).  One *step* = one `RungeKutta<3>::Update`
+(3 stages, each one residual + stage update) preceded by `GetTimeStep`, as in the reference's time
+loop (demo/euler/sourceless.cpp:187-215).  value = 3 * n_dof_total * steps / time.
+
+Workload (config 2 of BASELINE.json): synthetic structured box of 42^3 Hexahedron8 cells per GPU
+(10 001 880 DOF at p=2, K=5), FR-Lobatto p=2, HLLC, isentropic-vortex initial state, periodic
+wrap (the GPU-only performance variant), RK3.  N > 1: weak scaling, one 42^3
+block per GPU in a px*py*pz block partition, ghost-cell exchange over NCCL.
+
+Arms:
+  (default)          our CUDA path.  `value`: state resident in HBM.  `e2e`: the same step through the
+                     System interface with HOST columns: SetSolutionColumn(pinned host) -> GetTimeStep
+                     -> Update -> GetSolutionColumn(pinned host) every step.
+  --impl reference   the reference's own CPU code (oracle/_ref: unmodified headers behind
+                     oracle/ref_harness.cpp; falls back to the C restatement when it was not shipped),
+                     all host threads, on a bounded sample of the workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+B_ALG_P2 = 24.0 + 192.0 / 135.0   # algorithmic bytes per DOF-update
+RIEMANN = {"exact": 0, "hllc": 1, "ausm": 2}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cells", type=int, default=42, help="cells per direction per GPU")
+    ap.add_argument("--degree", type=int, default=2)
+    ap.add_argument("--riemann", default="hllc", choices=list(RIEMANN))
+    ap.add_argument("--scheme", default="fr", choices=["fr", "dg"])
+    ap.add_argument("--cpu-cells", type=int, default=0, help="cells per direction of the CPU sample (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------------------------
+# clocks
+# ---------------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.samples, self._stop = index, [], threading.Event()
+        self.thread = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                parts = [p.strip() for p in out.strip().split(",")]
+                if len(parts) >= 6:
+                    self.samples.append(parts)
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def __enter__(self):
+        self.thread.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self.thread.join(timeout=6)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm = sorted(float(s[0]) for s in self.samples)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.samples[0][1]), "reasons": reasons,
+                "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------
+# reference arm / cpu baseline
+# ---------------------------------------------------------------------------------------------------
+def cpu_run(args, steps, warmup, cells=None):
+    """Times the reference's CPU implementation (oracle/_ref) — or the C restatement when the
+    reference binary is absent — on a bounded sample: an n^3 box of the same cells, same scheme, same
+    Riemann solver, vortex state, inviscid walls instead of the periodic wrap (the reference has no
+    periodic boundary), block-partitioned over all host cores (one thread per part, in-process halo)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_check as oc
+    import refapi
+    from minicfd_b200 import mesh as meshmod
+    from minicfd_b200.part import cell_points
+    cores = os.cpu_count() or 1
+    scheme = 0 if args.scheme == "fr" else 1
+    riemann = RIEMANN[args.riemann]
+    kf = 5 * (args.degree + 1) ** 3
+    if refapi.available(args.degree):
+        kind = "reference"
+        n_parts = max(1, min(cores, 64))
+        # ~8e6 DOF-updates/s/core; aim at ~1.5 s per step
+        n = cells or args.cpu_cells or int(round((n_parts * 8e6 * 1.5 / (3 * kf)) ** (1 / 3)))
+        n = max(6, min(n, 48))
+        m = meshmod.box(n, n, n, hi=(10.0, 10.0, 10.0))
+        px, py, pz = meshmod.factor3(n_parts)
+        parts = meshmod.block_partition(m, px, py, pz)
+        r = refapi.Ref(m, degree=args.degree, scheme=scheme, riemann=riemann, cell_parts=parts, n_parts=n_parts)
+        for tag in range(6):
+            r.set_bc(tag, refapi.WALL)
+        r.approximate(refapi.F_VORTEX, [5.0, 5.0, 1.0, 1.0, 0.0, 5.0])
+        dt = r.time_step(1.0, 3)
+        step = lambda: r.rk_update(3, 0.0, r.time_step(1.0, 3), 1)  # noqa: E731
+    else:
+        kind = "port"
+        n_parts = 1
+        n = cells or args.cpu_cells or 12
+        m = meshmod.box(n, n, n, hi=(10.0, 10.0, 10.0))
+        o = oc.Oracle(m, args.degree, scheme, riemann)
+        for tag in range(6):
+            o.set_bc(tag, 0)
+        state = {"u": o.approximate(oc.F_VORTEX, [5.0, 5.0, 1.0, 1.0, 0.0, 5.0])}
+
+        def step():
+            dt = o.time_step(state["u"], 1.0, 3)
+            state["u"] = o.rk_update(state["u"], 3, 0.0, dt)
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt_wall = time.perf_counter() - t0
+    n_dof = m.n_cells * kf
+    value = 3.0 * n_dof * steps / dt_wall
+    sample = (f"{n}^3 Hexahedron8 cells ({n_dof} DOF), {args.scheme.upper()}-Lobatto p={args.degree}, "
+              f"{args.riemann}, RK3 incl. GetTimeStep, inviscid walls, {n_parts} part(s)/thread(s), "
+              f"{steps} step(s) after {warmup} warm-up")
+    return {"value": value, "unit": "DOF-updates/s", "cores": n_parts, "kind": kind, "sample": sample,
+            "host_cores": cores, "ms_per_step": 1e3 * dt_wall / steps}
+
+
+def config_dict(args, n_gpus, dims, part):
+    return {"workload": f"BASELINE config 2: synthetic structured box, {dims[0]}x{dims[1]}x{dims[2]} Hexahedron8 "
+                        f"cells total ({args.cells}^3 per GPU), Euler isentropic vortex, "
+                        f"{args.scheme.upper()}-Lobatto p={args.degree}, {args.riemann.upper()}, RK3, periodic",
+            "cells_per_gpu": args.cells ** 3, "dof_per_gpu": args.cells ** 3 * 5 * (args.degree + 1) ** 3,
+            "step": "GetTimeStep + RungeKutta<3>::Update (3 stages)", "parallelism": f"domain decomposition {part}",
+            "l2_policy": "state (3 x 80 MB per GPU) exceeds the 126 MB L2; no flush needed"}
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
+    # bound the whole run to a few minutes: the sample is sized for ~1.5 s per step
+    steps_run, warm_run = min(steps, 10), min(warmup, 2)
+    res = cpu_run(args, steps_run, warm_run)
+    px, py, pz = __import__("minicfd_b200.mesh", fromlist=["factor3"]).factor3(args.gpus)
+    dims = (args.cells * px, args.cells * py, args.cells * pz)
+    line = {"impl": "reference", "metric": "DOF-updates/s per RK stage (p=2 Euler, hexa)",
+            "value": res["value"], "unit": "DOF-updates/s", "n_gpus": args.gpus, "steps": steps_run,
+            "warmup": warm_run, "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": config_dict(args, args.gpus, dims, f"{px}x{py}x{pz}"),
+            "cpu_baseline": {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": res["value"], "unit": "DOF-updates/s", "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+# ---------------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------------
+def ours(args):
+    import torch
+    import torch.distributed as dist
+    from minicfd_b200 import capi, fields, halo, mesh as meshmod
+    from minicfd_b200.part import Part
+    from minicfd_b200.spatial import RungeKutta, Spatial
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the CUDA path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    px, py, pz = meshmod.factor3(world)
+    n = args.cells
+    dims = (n * px, n * py, n * pz)
+    m = meshmod.box(*dims, hi=(10.0 * px, 10.0 * py, 10.0 * pz), periodic=True)
+    parts = meshmod.block_partition(m, px, py, pz) if world > 1 else None
+    part = Part(m, parts, rank, world)
+    scheme = capi.FR_LOBATTO if args.scheme == "fr" else capi.DG_LOBATTO
+    comm = halo.for_part(part, 5 * (args.degree + 1) ** 3) if world > 1 else None
+    sp = Spatial(part, scheme=scheme, degree=args.degree, riemann=RIEMANN[args.riemann], device=local_rank,
+                 comm=comm)
+    sp.ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+    sp.Approximate(lambda x: fields.vortex()(x, 0.0))
+    if comm is not None:
+        comm.exchange()
+    rk = RungeKutta(3)
+    n_dof_local = part.n_local * sp.kfields
+    n_dof_total = n_dof_local * world
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_device(t):
+        dt = sp.GetTimeStep(1.0, 3)
+        rk.Update(sp, t, dt)
+        return dt
+
+    t = 0.0
+    for _ in range(max(args.warmup, 3)):
+        t += step_device(t)
+    sp.ctx.enable_kernel_timing(True)
+    launches0 = sp.ctx.launch_count()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clocks:
+        e0.record()
+        for _ in range(args.steps):
+            t += step_device(t)
+        e1.record()
+        barrier()
+    ms = e0.elapsed_time(e1)
+    kernel_ms, kernel_launches = sp.ctx.kernel_time(reset=True)
+    sp.ctx.enable_kernel_timing(False)
+    launches = sp.ctx.launch_count() - launches0
+    tmax = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    ms = float(tmax.item())
+    value = 3.0 * n_dof_total * args.steps / (ms * 1e-3)
+
+    # ---- e2e: host columns in and out every step ---------------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        host_in = torch.empty(n_dof_local, dtype=torch.float64, pin_memory=True)
+        host_out = torch.empty(n_dof_local, dtype=torch.float64, pin_memory=True)
+        host_in.numpy()[:] = sp.GetSolutionColumn()
+        e_steps = max(3, min(args.steps, 10))
+
+        def step_e2e(tt):
+            sp.ctx.set_solution(host_in.numpy())          # H2D from pinned memory
+            if comm is not None:
+                pass                                      # ghosts are refreshed inside Update
+            dt = sp.GetTimeStep(1.0, 3)
+            rk.Update(sp, tt, dt)
+            sp.ctx.get_solution(host_out.numpy())         # D2H of the step's result
+            host_in.copy_(host_out)
+            return dt
+        for _ in range(2):
+            t += step_e2e(t)
+        barrier()
+        t0 = time.perf_counter()
+        e0.record()
+        for _ in range(e_steps):
+            t += step_e2e(t)
+        e1.record()
+        barrier()
+        ms_e = max(e0.elapsed_time(e1), 1e3 * (time.perf_counter() - t0))
+        tm = torch.tensor([ms_e], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        e2e = {"value": 3.0 * n_dof_total * e_steps / (float(tm.item()) * 1e-3), "unit": "DOF-updates/s",
+               "h2d_bytes_per_step": n_dof_local * 8, "d2h_bytes_per_step": n_dof_local * 8 + 8,
+               "steps": e_steps}
+
+    if rank == 0:
+        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(peaks_path):
+            peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        else:
+            peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+        b_alg = 24.0 + 192.0 / sp.kfields
+        per_launch_ms = kernel_ms / max(kernel_launches, 1)
+        # one launch per stage when there is no ghost layer; with ghosts a stage is two launches
+        launches_per_stage = kernel_launches / (3.0 * args.steps)
+        achieved = b_alg * n_dof_local / (per_launch_ms * launches_per_stage * 1e-3) / 1e9
+        roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                    "traffic": None, "peak_source": peak_src, "kernel": "mcfd::StageKernel",
+                    "algorithmic_bytes_per_dof_update": b_alg, "kernel_ms_per_stage": per_launch_ms * launches_per_stage,
+                    "kernel_share_of_step": kernel_ms / ms}
+        traffic_path = os.path.join(ROOT, "profiles", "stage_kernel_traffic.json")
+        if os.path.exists(traffic_path):
+            roofline["traffic"] = json.load(open(traffic_path)).get("dram_bytes_per_launch")
+        line = {"metric": "DOF-updates/s per RK stage (p=2 Euler, hexa)", "value": value, "unit": "DOF-updates/s",
+                "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": config_dict(args, world, dims, f"{px}x{py}x{pz}"), "clocks": clocks.summary(),
+                "roofline": roofline, "gpu_launches": int(launches)}
+        if e2e is not None:
+            line["e2e"] = e2e
+        if world == 1 and not args.no_cpu_baseline:
+            res = cpu_run(args, steps=3, warmup=1)
+            line["cpu_baseline"] = {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        ours(args)
+
+
+if __name__ == "__main__":
+    main()
