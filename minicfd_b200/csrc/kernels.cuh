@@ -189,6 +189,24 @@ MCFD_HD void StagePhaseA(const StageArgs &p, int tid, int bid, double *smem) {
 }
 
 // ---- phase B: divergence + face corrections + 1/det + RK update --------------------------------
+template <class T>
+MCFD_HD T Sel3(int d, T a0, T a1, T a2) { return d == 0 ? a0 : (d == 1 ? a1 : a2); }
+
+// The neighbour's coefficients at the node facing my face point (or zeros when there is none).
+template <int F, int FQ>
+MCFD_HD void GatherNeighbour(const StageArgs &p, const unsigned char *sNbrNode, int q, int nb, int code,
+    double *v) {
+  if (q >= 0 && nb >= 0) {
+    const int n2 = sNbrNode[((code & 7) * 8 + ((code >> 3) & 7)) * FQ + q];
+    const double *src = p.u_in + ((size_t)(nb >> 5) * F + n2 * 5) * kTile + (nb & 31);
+#pragma unroll
+    for (int c = 0; c < 5; ++c) v[c] = src[c * kTile];
+  } else {
+#pragma unroll
+    for (int c = 0; c < 5; ++c) v[c] = 0;
+  }
+}
+
 template <int Q, int kRiemann, int CPB, int NW>
 MCFD_HD void StagePhaseB(const StageArgs &p, int tid, int bid, double *smem) {
   using G = StageGeometry<Q, CPB, NW>;
@@ -197,81 +215,124 @@ MCFD_HD void StagePhaseB(const StageArgs &p, int tid, int bid, double *smem) {
   if (!g.active) return;
   const int tile = g.tile, tl = g.tl, lc = g.lc;
   const double *uin = p.u_in + (size_t)tile * F * kTile + tl;
+  const double *u0p = p.u0 + (size_t)tile * F * kTile + tl;
+  double *out = p.u_out + (size_t)tile * F * kTile + tl;
+  const bool need_u0 = p.mode >= kModeRk3b;
 #pragma unroll 1
   for (int s = 0; s < G::SLOTS; ++s) {
-    int n = g.Node(s);
+    const int n = g.Node(s);
     if (n < 0) continue;
-    int ijk[3] = {n / FQ, (n / Q) % Q, n % Q};
-    const int stride[3] = {FQ, Q, 1};
-    double r[5] = {0, 0, 0, 0, 0};
-    // flux divergence along the three node lines (fr/general.hpp:280-286; dg/lobatto.hpp:161-170)
+    const int i0 = n / FQ, i1 = (n / Q) % Q, i2 = n % Q;
+    // issue every global load of this node up front: own state, u0, face descriptors
+    double u[5], u0[5];
+#pragma unroll
+    for (int c = 0; c < 5; ++c) u[c] = uin[(n * 5 + c) * kTile];
+#pragma unroll
+    for (int c = 0; c < 5; ++c) u0[c] = need_u0 ? u0p[(n * 5 + c) * kTile] : 0.0;
+    int fq[3], fnb[3], fcode[3];
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
-      int base = n - ijk[d] * stride[d];
+      const int id = d == 0 ? i0 : (d == 1 ? i1 : i2);
+      fq[d] = c_tab.node_q[n][d];
+      const bool plus = id != 0;                   // faces 2,3,5 are the +1 sides
+      const int f = (d == 0) ? (plus ? 2 : 4) : (d == 1) ? (plus ? 3 : 1) : (plus ? 5 : 0);
+      fnb[d] = 0; fcode[d] = 0;
+      if (fq[d] >= 0) {
+        fnb[d] = p.nbr[((size_t)tile * 6 + f) * kTile + tl];
+        fcode[d] = p.code[((size_t)tile * 6 + f) * kTile + tl];
+      }
+    }
+    double vcur[5], vnext[5];
+    GatherNeighbour<F, FQ>(p, g.sNbrNode, fq[0], fnb[0], fcode[0], vcur);
+    // flux divergence along the three node lines (fr/general.hpp:280-286; dg/lobatto.hpp:161-170)
+    double r[5] = {0, 0, 0, 0, 0};
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      const int id = d == 0 ? i0 : (d == 1 ? i1 : i2);
+      const int st = d == 0 ? FQ : (d == 1 ? Q : 1);
+      const int base = n - id * st;
 #pragma unroll
       for (int mm = 0; mm < Q; ++mm) {
-        double a = c_tab.a[ijk[d]][mm];
-        const double *src = g.sF + ((size_t)(base + mm * stride[d]) * 15 + d * 5) * CPB + lc;
+        const double a = c_tab.a[id][mm];
+        const double *src = g.sF + ((size_t)(base + mm * st) * 15 + d * 5) * CPB + lc;
 #pragma unroll
         for (int c = 0; c < 5; ++c) r[c] = fma(a, src[c * CPB], r[c]);
       }
     }
-    double u[5];
-#pragma unroll
-    for (int c = 0; c < 5; ++c) u[c] = uin[(n * 5 + c) * kTile];
-    Metric m = ComputeMetric(g.sG + lc, CPB, c_tab.xi[ijk[0]], c_tab.xi[ijk[1]], c_tab.xi[ijk[2]]);
+    const Metric m = ComputeMetric(g.sG + lc, CPB, c_tab.xi[i0], c_tab.xi[i1], c_tab.xi[i2]);
     // face corrections (fr/lobatto.hpp:232-251, 278-428; fr/general.hpp:296-315; dg/lobatto.hpp:171-191)
-#pragma unroll
+    // One rolled loop (a single copy of the Riemann solver in the instruction stream); the next
+    // face's neighbour state is requested before the current face is solved.
+#pragma unroll 1
     for (int d = 0; d < 3; ++d) {
-      int q = c_tab.node_q[n][d];
-      if (q < 0) continue;
-      const bool plus = ijk[d] != 0;               // faces 2,3,5 are the +1 sides
-      const int f = (d == 0) ? (plus ? 2 : 4) : (d == 1) ? (plus ? 3 : 1) : (plus ? 5 : 0);
-      const int nb = p.nbr[((size_t)tile * 6 + f) * kTile + tl];
-      const double sgn = plus ? 1.0 : -1.0;
-      double nx = m.s[d][0], ny = m.s[d][1], nz = m.s[d][2];
-      double area = sqrt(nx * nx + ny * ny + nz * nz);
-      double inv = sgn / area;
-      nx *= inv; ny *= inv; nz *= inv;             // outward unit normal
-      double fl[5];
-      if (nb >= 0) {
-        const int code = p.code[((size_t)tile * 6 + f) * kTile + tl];
-        const int n2 = g.sNbrNode[((code & 7) * 8 + ((code >> 3) & 7)) * FQ + q];
-        const double *src = p.u_in + ((size_t)(nb >> 5) * F + n2 * 5) * kTile + (nb & 31);
-        double v[5];
-#pragma unroll
-        for (int c = 0; c < 5; ++c) v[c] = src[c * kTile];
-        if (code & 64) {  // I hold this face: normal points from me to the neighbour
-          FluxUpwind<kRiemann>(u, v, nx, ny, nz, fl);
-        } else {          // evaluate in the holder's frame, as the reference does
-          FluxUpwind<kRiemann>(v, u, -nx, -ny, -nz, fl);
-#pragma unroll
-          for (int c = 0; c < 5; ++c) fl[c] = -fl[c];
-        }
-      } else {
-        const int b = -1 - nb;
-        const int kind = p.bkind[b];
-        if (kind == kBcNoSlip) continue;
-        BoundaryFlux<kRiemann>(kind, u, p.bvals + ((size_t)b * FQ + q) * 5, nx, ny, nz, fl);
+      const int q = Sel3(d, fq[0], fq[1], fq[2]);
+      const int nb = Sel3(d, fnb[0], fnb[1], fnb[2]);
+      const int code = Sel3(d, fcode[0], fcode[1], fcode[2]);
+      if (d < 2) {
+        GatherNeighbour<F, FQ>(p, g.sNbrNode, Sel3(d + 1, fq[0], fq[1], fq[2]), Sel3(d + 1, fnb[0], fnb[1], fnb[2]),
+            Sel3(d + 1, fcode[0], fcode[1], fcode[2]), vnext);
       }
-      const double cf = c_tab.coef_f * area, cF = c_tab.coef_F * sgn;
-      const double *own = g.sF + ((size_t)n * 15 + d * 5) * CPB + lc;
+      if (q >= 0) {
+        const int id = Sel3(d, i0, i1, i2);
+        const double sgn = id != 0 ? 1.0 : -1.0;
+        double nx = Sel3(d, m.s[0][0], m.s[1][0], m.s[2][0]);
+        double ny = Sel3(d, m.s[0][1], m.s[1][1], m.s[2][1]);
+        double nz = Sel3(d, m.s[0][2], m.s[1][2], m.s[2][2]);
+        const double area = sqrt(nx * nx + ny * ny + nz * nz);
+        const double inv = sgn / area;
+        nx *= inv; ny *= inv; nz *= inv;           // outward unit normal
+        double fl[5];
+        bool skip = false;
+        if (nb >= 0) {
+          // The Riemann problem is posed in the holder's frame, as the reference does: when the
+          // neighbour holds the face, swap the states, flip the normal and negate the result.
+          const bool holder = (code & 64) != 0;
+          const double hs = holder ? 1.0 : -1.0;
+          double ul[5], ur[5];
 #pragma unroll
-      for (int c = 0; c < 5; ++c) r[c] = fma(cF, own[c * CPB], fma(-cf, fl[c], r[c]));
+          for (int c = 0; c < 5; ++c) {
+            ul[c] = holder ? u[c] : vcur[c];
+            ur[c] = holder ? vcur[c] : u[c];
+          }
+          FluxUpwind<kRiemann>(ul, ur, hs * nx, hs * ny, hs * nz, fl);
+#pragma unroll
+          for (int c = 0; c < 5; ++c) fl[c] *= hs;
+        } else {
+          const int b = -1 - nb;
+          const int kind = p.bkind[b];
+          skip = kind == kBcNoSlip;
+          if (!skip) {
+            State5 ui, given;
+            const double *gv = p.bvals + ((size_t)b * FQ + q) * 5;
+#pragma unroll
+            for (int c = 0; c < 5; ++c) { ui.v[c] = u[c]; given.v[c] = gv[c]; }
+            const State5 bf = BoundaryFluxOutOfLine<kRiemann>(kind, ui, given, nx, ny, nz);
+#pragma unroll
+            for (int c = 0; c < 5; ++c) fl[c] = bf.v[c];
+          }
+        }
+        if (!skip) {
+          const double cf = c_tab.coef_f * area, cF = c_tab.coef_F * sgn;
+          const double *own = g.sF + ((size_t)n * 15 + d * 5) * CPB + lc;
+#pragma unroll
+          for (int c = 0; c < 5; ++c) r[c] = fma(cF, own[c * CPB], fma(-cf, fl[c], r[c]));
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < 5; ++c) vcur[c] = vnext[c];
     }
     const double inv_det = 1.0 / m.det;            // fr/general.hpp:256-266; dg/lobatto.hpp:143-158
-    double *out = p.u_out + (size_t)tile * F * kTile + tl;
-    const double *u0 = p.u0 + (size_t)tile * F * kTile + tl;
+    const double dt = p.dt;
 #pragma unroll
     for (int c = 0; c < 5; ++c) {
-      double res = r[c] * inv_det;
+      const double res = r[c] * inv_det;
       double val;
       switch (p.mode) {
       case kModeResidual: val = res; break;
-      case kModeEuler: val = u[c] + res * p.dt; break;
-      case kModeRk3b: val = (u0[(n * 5 + c) * kTile] * 3 + (u[c] + res * p.dt)) * 0.25; break;
-      case kModeRk3c: val = ((u[c] + res * p.dt) * 2 + u0[(n * 5 + c) * kTile]) / 3; break;
-      default: val = ((u[c] + res * p.dt) + u0[(n * 5 + c) * kTile]) * 0.5; break;
+      case kModeEuler: val = u[c] + res * dt; break;
+      case kModeRk3b: val = (u0[c] * 3 + (u[c] + res * dt)) * 0.25; break;
+      case kModeRk3c: val = ((u[c] + res * dt) * 2 + u0[c]) / 3; break;
+      default: val = ((u[c] + res * dt) + u0[c]) * 0.5; break;
       }
       out[(n * 5 + c) * kTile] = val;
     }

@@ -309,7 +309,8 @@ int mcfd_set_mesh(mcfd_ctx *ctx, int64_t n_nodes, const double *xyz, int64_t n_l
     for (int f = 0; f < 6; ++f)
       if (ctx->mesh.nbr[c * 6 + f] >= n_local) { first_inter = c; break; }
   ctx->total_blocks = (n_local + ctx->cpb - 1) / ctx->cpb;
-  ctx->inner_blocks = first_inter / ctx->cpb;
+  // without ghosts the whole part goes in one launch; with ghosts only full blocks of inner cells
+  ctx->inner_blocks = (n_ghost == 0) ? ctx->total_blocks : first_inter / ctx->cpb;
   ctx->send_cells.Free(); ctx->recv_cells.Free(); ctx->send_buf.Free(); ctx->recv_buf.Free();
   ctx->cur = 0;
   ctx->has_mesh = true;

@@ -13,10 +13,12 @@
 #ifdef __CUDACC__
 #include <cuda_runtime.h>
 #define MCFD_HD __device__ __forceinline__
+#define MCFD_NOINLINE __device__ __noinline__
 #define MCFD_CONSTANT __constant__
 #else  // host build of the same source: tests/host_emulation only
 #include <cmath>
 #define MCFD_HD inline
+#define MCFD_NOINLINE inline
 #define MCFD_CONSTANT static
 using std::fma; using std::fmax; using std::fmin; using std::pow; using std::sqrt;
 #endif
@@ -36,6 +38,10 @@ constexpr double kOneOverGamma = 1 / kGamma;
 constexpr double kGammaOverGm1 = kGamma / kGm1;
 
 enum : int { kExact = 0, kHllc = 1, kAusm = 2 };
+
+// pow() expands to several hundred instructions; one shared copy keeps the stage kernel's hot loop
+// inside the instruction cache.
+MCFD_NOINLINE double Pow(double x, double y) { return pow(x, y); }
 
 struct Prim {
   double rho, u, v, w, p;  // velocity in the global frame
@@ -182,7 +188,7 @@ struct SpeedChange {  // exact.hpp:153-200
       return (pa - p_b) / sqrt(rho_b * P(pa));
     }
     constexpr double e = kGm1Over2 / kGamma;
-    return (pow(pa / p_b, e) - 1) * (kGm1Under2 * a_b);
+    return (Pow(pa / p_b, e) - 1) * (kGm1Under2 * a_b);
   }
   MCFD_HD double Prime(double pa) const {
     if (pa >= p_b) {
@@ -191,7 +197,7 @@ struct SpeedChange {  // exact.hpp:153-200
       return (1 + v / pp) / sqrt(rho_b * pp);
     }
     constexpr double e = -kGp1Over2 / kGamma;
-    return pow(pa / p_b, e) / (rho_b * a_b);
+    return Pow(pa / p_b, e) / (rho_b * a_b);
   }
 };
 
@@ -203,7 +209,7 @@ MCFD_HD Rup InsideExpansion(double gri_1, double gri_2) {  // exact.hpp:255-266
   constexpr double r = kGm1 / (kGamma + 1);
   double a = r * gri_2;
   double a2 = a * a;
-  double rho = pow(a2 / gri_1 * kOneOverGamma, kOneOverGm1);
+  double rho = Pow(a2 / gri_1 * kOneOverGamma, kOneOverGm1);
   return Rup{rho, a, a2 * rho * kOneOverGamma};
 }
 
@@ -233,7 +239,7 @@ MCFD_HD Rup NearExpansion(double rb, double ub, double pb, double us, double ps)
   if (before) {
     return Rup{rb, ub, pb};
   }
-  double gri_1 = pb / pow(rb, kGamma);
+  double gri_1 = pb / Pow(rb, kGamma);
   double gri_2 = (kField == 1) ? ub + kGm1Under2 * a_before : ub - kGm1Under2 * a_before;
   return InsideExpansion(gri_1, gri_2);
 }
@@ -251,7 +257,7 @@ MCFD_HD Rup SolveExactAxis(double rl, double ul, double pl,
       if (ul >= al) return Rup{rl, ul, pl};
       double us = ul + al * kGm1Under2;
       if (us <= 0) return Rup{0, 0, 0};
-      return InsideExpansion(pl / pow(rl, kGamma), us);
+      return InsideExpansion(pl / Pow(rl, kGamma), us);
     }
   } else {
     if (rr > 0) {  // only left vacuum (exact.hpp:85-98)
@@ -259,7 +265,7 @@ MCFD_HD Rup SolveExactAxis(double rl, double ul, double pl,
       if (ur + ar <= 0) return Rup{rr, ur, pr};
       double us = ur - ar * kGm1Under2;
       if (us >= 0) return Rup{0, 0, 0};
-      return InsideExpansion(pr / pow(rr, kGamma), us);
+      return InsideExpansion(pr / Pow(rr, kGamma), us);
     }
     return Rup{0, 0, 0};
   }
@@ -290,10 +296,10 @@ MCFD_HD Rup SolveExactAxis(double rl, double ul, double pl,
   if (ul > al) return Rup{rl, ul, pl};
   double ar = SoundSpeed(rr, pr);
   if (ur + ar < 0) return Rup{rr, ur, pr};
-  double gri_1 = pl / pow(rl, kGamma);
+  double gri_1 = pl / Pow(rl, kGamma);
   double gri_2 = ul + al * kGm1Under2;
   if (gri_2 >= 0) return InsideExpansion(gri_1, gri_2);
-  gri_1 = pr / pow(rr, kGamma);
+  gri_1 = pr / Pow(rr, kGamma);
   gri_2 = ur - ar * kGm1Under2;
   if (gri_2 < 0) return InsideExpansion(gri_1, gri_2);
   return Rup{0, 0, 0};
@@ -396,7 +402,7 @@ MCFD_HD void BoundaryFlux(int kind, const double *ui, const double *given,
     double c_b = fmax((-qb_half + sqrt_delta) / qa, (-qb_half - sqrt_delta) / qa);
     double t_b = c_b * c_b / gamma_r;
     double mach_b = sqrt((t_total / t_b - 1) / kGm1Over2);
-    double p_b = given[0] / pow(1 + kGm1Over2 * mach_b * mach_b, kGammaOverGm1);
+    double p_b = given[0] / Pow(1 + kGm1Over2 * mach_b * mach_b, kGammaOverGm1);
     double speed = mach_b * c_b;
     Prim b;
     b.p = p_b;
@@ -419,6 +425,21 @@ MCFD_HD void BoundaryFlux(int kind, const double *ui, const double *given,
   default:  // kBcNoSlip: no-op for inviscid systems (fem.hpp:382-383) -> caller skips
     flux[0] = flux[1] = flux[2] = flux[3] = flux[4] = 0;
   }
+}
+
+struct State5 {
+  double v[5];
+};
+
+// Out-of-line boundary flux with by-value arguments: keeps the (rare) boundary code, incl. its own
+// copy of the Riemann solver for the smart boundary, out of the interior-face instruction stream
+// without forcing the caller's state arrays into local memory.
+template <int kRiemann>
+MCFD_NOINLINE State5 BoundaryFluxOutOfLine(int kind, State5 ui, State5 given, double nx, double ny,
+    double nz) {
+  State5 f;
+  BoundaryFlux<kRiemann>(kind, ui.v, given.v, nx, ny, nz, f.v);
+  return f;
 }
 
 }  // namespace mcfd

@@ -81,12 +81,14 @@ def test_against_reference_binary_many_steps(degree, riemann):
     r = refapi.Ref(m, degree=degree, scheme=refapi.FR, riemann=riemann)
     cases.apply_bcs_ref(r, {t: cases.WALL for t in range(6)})
     sp = make_spatial(m, degree, capi.FR_LOBATTO, riemann)
-    u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), seed=5)
+    # a gentle state and a small dt_guess: the run stays smooth (no clipped negative-pressure
+    # states, whose handling in the reference returns uninitialised fluxes, hllc.hpp:34-43)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), seed=5, amp=1e-4)
     r.set_solution(u)
     sp.SetSolutionColumn(u)
     t = 0.0
     for _ in range(10):
-        dt_ref, dt = r.time_step(1.0, 3), sp.GetTimeStep(1.0, 3)
+        dt_ref, dt = r.time_step(4e-3, 3), sp.GetTimeStep(4e-3, 3)
         assert dt == pytest.approx(dt_ref, rel=1e-12)
         r.rk_update(3, t, dt_ref, 1)
         RungeKutta(3).Update(sp, t, dt_ref)
@@ -171,8 +173,9 @@ def test_two_parts_on_one_gpu_with_halo_buffers():
     bufs = []
     for sp in S:
         (s_ptr, s_n), (r_ptr, r_n) = sp.ctx.halo_buffers()
-        assert s_n == r_n > 0
+        assert s_n > 0 and r_n > 0
         bufs.append((s_ptr, s_n, r_ptr, r_n))
+    assert bufs[0][1] == bufs[1][3] and bufs[1][1] == bufs[0][3]
 
     def exchange():
         from minicfd_b200.halo import _DeviceArray
