@@ -25,6 +25,11 @@ constexpr int kMaxN = kMaxQ * kMaxQ * kMaxQ;
 constexpr int kMaxFaceQ = kMaxQ * kMaxQ;
 constexpr int kMaxSlots = 8;    // node slots per warp
 constexpr int kMaxWarps = 16;
+// launch shape per degree: cells per CTA and warps per CTA (see StageKernel)
+#ifndef MCFD_P2_WARPS
+#define MCFD_P2_WARPS 8
+#endif
+constexpr int kP2Cells = 32, kP2Warps = MCFD_P2_WARPS, kP3Cells = 16, kP3Warps = 16;
 
 // Per-degree tables, filled by the host (tables.cpp) and copied to constant memory.
 struct Tables {
@@ -37,6 +42,8 @@ struct Tables {
   signed char node_q[kMaxN][3];
   // neighbour node for (sharer face f', orientation o, my face-point q)
   unsigned char nbr_node[6][8][kMaxFaceQ];
+  // cell node of face point q of local face f
+  unsigned char face_node[6][kMaxFaceQ];
 };
 
 struct StageArgs {
@@ -95,28 +102,65 @@ MCFD_HD Metric ComputeMetric(const double *g, int gs, double x, double e, double
   return m;
 }
 
+template <class T>
+MCFD_HD T Sel3(int d, T a0, T a1, T a2) { return d == 0 ? a0 : (d == 1 ? a1 : a2); }
+
+// Column d of J* only (the un-normalised normal of the d-faces at this node).
+MCFD_HD void ComputeNormal(const double *g, int gs, double x, double e, double z, int d, double *n) {
+  double r[3][3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    double c1 = g[(0 + k) * gs], c2 = g[(3 + k) * gs], c3 = g[(6 + k) * gs];
+    double c4 = g[(9 + k) * gs], c5 = g[(12 + k) * gs], c6 = g[(15 + k) * gs], c7 = g[(18 + k) * gs];
+    r[0][k] = fma(z, fma(e, c7, c6), fma(e, c4, c1));
+    r[1][k] = fma(z, fma(x, c7, c5), fma(x, c4, c2));
+    r[2][k] = fma(e, fma(x, c7, c5), fma(x, c6, c3));
+  }
+  double a[3], b[3];   // rows (d+1)%3 and (d+2)%3
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    a[k] = Sel3(d, r[1][k], r[2][k], r[0][k]);
+    b[k] = Sel3(d, r[2][k], r[0][k], r[1][k]);
+  }
+  n[0] = a[1] * b[2] - a[2] * b[1];
+  n[1] = a[2] * b[0] - a[0] * b[2];
+  n[2] = a[0] * b[1] - a[1] * b[0];
+}
+
 // One RK stage (or a bare residual) for the cells of a CTA-sized block.
-//   CPB  cells per CTA: 32 (a whole tile, one node per warp at a time) or 16 (half a tile, two
-//        nodes per warp at a time) — bounded by the shared-memory flux cache of N*15*CPB doubles.
+//   CPB  cells per CTA: 32 (a whole tile: a warp handles one node or face point of 32 cells at a
+//        time) or 16 (half a tile, two per warp) — bounded by the shared-memory flux cache of
+//        N*15*CPB doubles.
 //   NW   warps per CTA.
+// Phases, separated by CTA barriers:
+//   A   node-centric     Fhat = F(u) J* at every node -> shared memory sF[N][15][CPB]
+//   B1  node-centric     R = (sum_lines a * Fhat  +  own-face Fhat terms) / det      (registers)
+//   --  sF is dead from here on and is reused: sR[N][5][CPB] then sC[6*Q*Q][5][CPB]
+//   B2  face-point-centric  one Riemann problem per face point -> lifted flux term -> sC
+//   C   node-centric     R + face terms, RK update, store
 // The body is written as per-thread phase functions of (thread id, block id, shared memory) so that
 // tests/host_emulation can run the very same source on the host to debug index logic without a GPU;
-// the __global__ kernel below strings them together with __syncthreads().
+// the __global__ kernel strings them together with __syncthreads().
 template <int Q, int CPB, int NW>
 struct StageGeometry {
   static constexpr int N = Q * Q * Q;
   static constexpr int F = 5 * N;
   static constexpr int FQ = Q * Q;
-  static constexpr int SUB = kTile / CPB;                 // nodes handled at once by a warp
+  static constexpr int SUB = kTile / CPB;                 // nodes / face points handled at once by a warp
   static constexpr int SLOTS = (N + NW * SUB - 1) / (NW * SUB);
+  static constexpr int POINTS = 6 * FQ;                   // face points per cell
+  static constexpr int ITEMS = (POINTS + NW * SUB - 1) / (NW * SUB);
   static constexpr size_t kSharedBytes =
       (size_t)(N * 15 * CPB + kGeomRows * CPB) * sizeof(double) + 6 * 8 * FQ;
+  static_assert(POINTS * 5 <= N * 10, "face terms must fit behind the residual rows");
   int lane, warp, lc, sub, block, tile, tl, cell;
   bool active;
-  double *sF, *sG;
+  double *sF, *sR, *sC, *sG;
   unsigned char *sNbrNode;
   MCFD_HD StageGeometry(const StageArgs &p, int tid, int bid, double *smem) {
     sF = smem;                                      // [N][15][CPB]
+    sR = smem;                                      // [N][5][CPB]        (after B1)
+    sC = smem + N * 5 * CPB;                        // [POINTS][5][CPB]   (after B1)
     sG = smem + N * 15 * CPB;                       // [21][CPB]
     sNbrNode = reinterpret_cast<unsigned char *>(sG + kGeomRows * CPB);  // [6][8][FQ]
     lane = tid & 31; warp = tid >> 5;
@@ -132,7 +176,42 @@ struct StageGeometry {
     int slot = (warp * SLOTS + s) * SUB + sub;
     return (slot < kMaxWarps * kMaxSlots) ? c_tab.slot_node[slot] : -1;
   }
+  // face point handled in item k: points are dealt round-robin so that all warps get the same count
+  MCFD_HD int Point(int k) const {
+    int pt = (k * NW + warp) * SUB + sub;
+    return pt < POINTS ? pt : -1;
+  }
 };
+
+MCFD_HD int FaceOf(int d, bool plus) {  // local face id of the -/+ side in direction d
+  return (d == 0) ? (plus ? 2 : 4) : (d == 1) ? (plus ? 3 : 1) : (plus ? 5 : 0);
+}
+
+template <int Q, int CPB, int NW>
+struct SlotStates {
+  double u[StageGeometry<Q, CPB, NW>::SLOTS][5];
+};
+template <int Q, int CPB, int NW>
+struct SlotResiduals {
+  double r[StageGeometry<Q, CPB, NW>::SLOTS][5];
+  double inv_det[StageGeometry<Q, CPB, NW>::SLOTS];
+};
+
+// All slots' loads are issued before the first use (and, on the GPU, before the prologue's barrier):
+// one memory latency per phase instead of one per slot.
+template <int Q, int CPB, int NW>
+MCFD_HD void StageLoadSlots(const StageArgs &p, int tid, int bid, double *smem, const double *src,
+    SlotStates<Q, CPB, NW> *st) {
+  using G = StageGeometry<Q, CPB, NW>;
+  G g(p, tid, bid, smem);
+  const double *uin = src + (size_t)g.tile * G::F * kTile + g.tl;
+#pragma unroll
+  for (int s = 0; s < G::SLOTS; ++s) {
+    const int n = g.Node(s);
+#pragma unroll
+    for (int c = 0; c < 5; ++c) st->u[s][c] = n >= 0 ? uin[(n * 5 + c) * kTile] : 0.0;
+  }
+}
 
 template <int Q, int CPB, int NW>
 MCFD_HD void StagePrologue(const StageArgs &p, int tid, int bid, double *smem) {
@@ -150,21 +229,23 @@ MCFD_HD void StagePrologue(const StageArgs &p, int tid, int bid, double *smem) {
 // ---- phase A: contravariant fluxes Fhat = F(u) J* at every node -> shared memory --------------
 // (fr/general.hpp:276-279; fem.hpp:392-395; types.hpp:322-333; polynomial/hexahedron.hpp:607-611)
 template <int Q, int CPB, int NW>
-MCFD_HD void StagePhaseA(const StageArgs &p, int tid, int bid, double *smem) {
+MCFD_HD void StagePhaseA(const StageArgs &p, int tid, int bid, double *smem,
+    const SlotStates<Q, CPB, NW> &st, SlotResiduals<Q, CPB, NW> *res) {
   using G = StageGeometry<Q, CPB, NW>;
   G g(p, tid, bid, smem);
-  constexpr int F = G::F, FQ = G::FQ;
-  const double *uin = p.u_in + (size_t)g.tile * F * kTile + g.tl;
-#pragma unroll 1
+  constexpr int FQ = G::FQ;
+#pragma unroll
   for (int s = 0; s < G::SLOTS; ++s) {
     int n = g.Node(s);
+    res->inv_det[s] = 0;
     if (n < 0) continue;
     int i = n / FQ, j = (n / Q) % Q, k = n % Q;
     double u[5];
 #pragma unroll
-    for (int c = 0; c < 5; ++c) u[c] = uin[(n * 5 + c) * kTile];
+    for (int c = 0; c < 5; ++c) u[c] = st.u[s][c];
     Prim q = ConsToPrim(u[0], u[1], u[2], u[3], u[4]);
     Metric m = ComputeMetric(g.sG + g.lc, CPB, c_tab.xi[i], c_tab.xi[j], c_tab.xi[k]);
+    res->inv_det[s] = Rcp(m.det);                  // fr/general.hpp:256-266; dg/lobatto.hpp:143-158
     double h0 = u[4] + q.p;
     double vel[3] = {q.u, q.v, q.w};
     double fx[3][5];  // flux matrix columns (x, y, z)
@@ -188,169 +269,256 @@ MCFD_HD void StagePhaseA(const StageArgs &p, int tid, int bid, double *smem) {
   }
 }
 
-// ---- phase B: divergence + face corrections + 1/det + RK update --------------------------------
-template <class T>
-MCFD_HD T Sel3(int d, T a0, T a1, T a2) { return d == 0 ? a0 : (d == 1 ? a1 : a2); }
+// ---- phase B1: flux divergence along the three node lines + the node's own face-flux terms ------
+// (fr/general.hpp:280-286, 290-294, 305-313; dg/lobatto.hpp:161-170)
+template <int Q, int CPB, int NW>
+MCFD_HD void StagePhaseB1(const StageArgs &p, int tid, int bid, double *smem, SlotResiduals<Q, CPB, NW> *res) {
+  using G = StageGeometry<Q, CPB, NW>;
+  G g(p, tid, bid, smem);
+  constexpr int FQ = G::FQ;
+  const int lc = g.lc;
+#pragma unroll
+  for (int s = 0; s < G::SLOTS; ++s) {
+    const int n = g.Node(s);
+    double r[5] = {0, 0, 0, 0, 0};
+    if (n >= 0) {
+      const int i0 = n / FQ, i1 = (n / Q) % Q, i2 = n % Q;
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        const int id = d == 0 ? i0 : (d == 1 ? i1 : i2);
+        const int st = d == 0 ? FQ : (d == 1 ? Q : 1);
+        const int base = n - id * st;
+#pragma unroll
+        for (int mm = 0; mm < Q; ++mm) {
+          const double a = c_tab.a[id][mm];
+          const double *src = g.sF + ((size_t)(base + mm * st) * 15 + d * 5) * CPB + lc;
+#pragma unroll
+          for (int c = 0; c < 5; ++c) r[c] = fma(a, src[c * CPB], r[c]);
+        }
+        if (id == 0 || id == Q - 1) {               // the node lies on a face in direction d
+          const double cF = id != 0 ? c_tab.coef_F : -c_tab.coef_F;
+          const double *own = g.sF + ((size_t)n * 15 + d * 5) * CPB + lc;
+#pragma unroll
+          for (int c = 0; c < 5; ++c) r[c] = fma(cF, own[c * CPB], r[c]);
+        }
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < 5; ++c) res->r[s][c] = r[c];
+  }
+}
 
-// The neighbour's coefficients at the node facing my face point (or zeros when there is none).
-template <int F, int FQ>
-MCFD_HD void GatherNeighbour(const StageArgs &p, const unsigned char *sNbrNode, int q, int nb, int code,
-    double *v) {
-  if (q >= 0 && nb >= 0) {
-    const int n2 = sNbrNode[((code & 7) * 8 + ((code >> 3) & 7)) * FQ + q];
-    const double *src = p.u_in + ((size_t)(nb >> 5) * F + n2 * 5) * kTile + (nb & 31);
+// after the barrier that retires sF: park the node residuals in shared memory
+template <int Q, int CPB, int NW>
+MCFD_HD void StageStoreResiduals(const StageArgs &p, int tid, int bid, double *smem,
+    const SlotResiduals<Q, CPB, NW> &res) {
+  using G = StageGeometry<Q, CPB, NW>;
+  G g(p, tid, bid, smem);
 #pragma unroll
-    for (int c = 0; c < 5; ++c) v[c] = src[c * kTile];
-  } else {
+  for (int s = 0; s < G::SLOTS; ++s) {
+    const int n = g.Node(s);
+    if (n < 0) continue;
 #pragma unroll
-    for (int c = 0; c < 5; ++c) v[c] = 0;
+    for (int c = 0; c < 5; ++c) g.sR[(n * 5 + c) * CPB + g.lc] = res.r[s][c];
+  }
+}
+
+// ---- phase B2: one Riemann problem per face point ------------------------------------------------
+// (fr/lobatto.hpp:232-251, 278-428; fr/general.hpp:296-315; dg/lobatto.hpp:171-191)
+struct PointLoads {   // everything a face point needs from global memory
+  double u[5], v[5];
+  int nb, code;
+};
+
+template <int Q, int CPB, int NW>
+MCFD_HD void LoadPoint(const StageArgs &p, const StageGeometry<Q, CPB, NW> &g, int pt, PointLoads *ld) {
+  constexpr int F = StageGeometry<Q, CPB, NW>::F, FQ = Q * Q;
+  ld->nb = -1; ld->code = 0;
+  if (pt < 0 || !g.active) return;      // the other fields are never read for such points
+  const int f = pt / FQ, q = pt % FQ;
+  const int n = c_tab.face_node[f][q];
+  const double *uin = p.u_in + (size_t)g.tile * F * kTile + g.tl;
+#pragma unroll
+  for (int c = 0; c < 5; ++c) ld->u[c] = uin[(n * 5 + c) * kTile];
+  ld->nb = p.nbr[((size_t)g.tile * 6 + f) * kTile + g.tl];
+  ld->code = p.code[((size_t)g.tile * 6 + f) * kTile + g.tl];
+  if (ld->nb >= 0) {
+    const int n2 = g.sNbrNode[((ld->code & 7) * 8 + ((ld->code >> 3) & 7)) * FQ + q];
+    const double *src = p.u_in + ((size_t)(ld->nb >> 5) * F + n2 * 5) * kTile + (ld->nb & 31);
+#pragma unroll
+    for (int c = 0; c < 5; ++c) ld->v[c] = src[c * kTile];
   }
 }
 
 template <int Q, int kRiemann, int CPB, int NW>
-MCFD_HD void StagePhaseB(const StageArgs &p, int tid, int bid, double *smem) {
+MCFD_HD void StagePhaseB2(const StageArgs &p, int tid, int bid, double *smem) {
+  using G = StageGeometry<Q, CPB, NW>;
+  G g(p, tid, bid, smem);
+  constexpr int FQ = G::FQ;
+  const int lc = g.lc;
+  PointLoads cur, next;
+  LoadPoint<Q, CPB, NW>(p, g, g.Point(0), &cur);
+#pragma unroll 1
+  for (int k = 0; k < G::ITEMS; ++k) {
+    const int pt = g.Point(k);
+    // request the next point's data before solving this one
+    LoadPoint<Q, CPB, NW>(p, g, (k + 1 < G::ITEMS) ? g.Point(k + 1) : -1, &next);
+    if (pt >= 0 && g.active) {
+      const int f = pt / FQ, q = pt % FQ;
+      const int n = c_tab.face_node[f][q];
+      const int d = (f == 2 || f == 4) ? 0 : ((f == 1 || f == 3) ? 1 : 2);
+      const double sgn = (f == 2 || f == 3 || f == 5) ? 1.0 : -1.0;
+      double nrm[3];
+      ComputeNormal(g.sG + lc, CPB, c_tab.xi[n / FQ], c_tab.xi[(n / Q) % Q], c_tab.xi[n % Q], d, nrm);
+      const double nx = nrm[0], ny = nrm[1], nz = nrm[2];
+      const double n2 = nx * nx + ny * ny + nz * nz;
+      const double inv_area = Rsqrt(n2), area = n2 * inv_area;
+      double fl[5];
+      double scale = -c_tab.coef_f * area;           // lifting coefficient; 1/det is applied in phase C
+      if (cur.nb >= 0) {
+        // The Riemann problem is posed in the holder's frame, as the reference does: when the
+        // neighbour holds the face, swap the states, flip the normal and negate the result.
+        const bool holder = (cur.code & 64) != 0;
+        const double hs = (holder ? sgn : -sgn) * inv_area;
+        double ul[5], ur[5];
+#pragma unroll
+        for (int c = 0; c < 5; ++c) {
+          ul[c] = holder ? cur.u[c] : cur.v[c];
+          ur[c] = holder ? cur.v[c] : cur.u[c];
+        }
+        FluxUpwind<kRiemann>(ul, ur, hs * nx, hs * ny, hs * nz, fl);
+        if (!holder) scale = -scale;
+      } else {
+        const int b = -1 - cur.nb;
+        const int kind = p.bkind[b];
+        const double inv = sgn * inv_area;
+        if (kind == kBcNoSlip) {
+          // no face term at all for inviscid systems (fem.hpp:382-383): cancel the node's own
+          // face-flux term that phase B1 has already added, -coef_F * sgn * (F(u) . J*col_d) / det
+          double fm[5][3];
+          Prim pr = ConsToPrim(cur.u[0], cur.u[1], cur.u[2], cur.u[3], cur.u[4]);
+          const double vel[3] = {pr.u, pr.v, pr.w};
+          const double h0 = cur.u[4] + pr.p;
+#pragma unroll
+          for (int x = 0; x < 3; ++x) {
+            fm[0][x] = cur.u[1 + x];
+            fm[1][x] = cur.u[1] * vel[x]; fm[2][x] = cur.u[2] * vel[x]; fm[3][x] = cur.u[3] * vel[x];
+            fm[1 + x][x] += pr.p;
+            fm[4][x] = h0 * vel[x];
+          }
+#pragma unroll
+          for (int c = 0; c < 5; ++c) fl[c] = fm[c][0] * nx + fm[c][1] * ny + fm[c][2] * nz;
+          scale = -c_tab.coef_F * sgn;
+        } else {
+          State5 ui, given;
+          const double *gv = p.bvals + ((size_t)b * FQ + q) * 5;
+#pragma unroll
+          for (int c = 0; c < 5; ++c) { ui.v[c] = cur.u[c]; given.v[c] = gv[c]; }
+          const State5 bf = BoundaryFluxOutOfLine<kRiemann>(kind, ui, given, inv * nx, inv * ny, inv * nz);
+#pragma unroll
+          for (int c = 0; c < 5; ++c) fl[c] = bf.v[c];
+        }
+      }
+      double *dst = g.sC + (size_t)pt * 5 * CPB + lc;
+#pragma unroll
+      for (int c = 0; c < 5; ++c) dst[c * CPB] = scale * fl[c];
+    }
+    cur = next;
+  }
+}
+
+// ---- phase C: gather the face terms, RK update, store ---------------------------------------------
+template <int Q, int CPB, int NW>
+MCFD_HD void StagePhaseC(const StageArgs &p, int tid, int bid, double *smem,
+    const SlotStates<Q, CPB, NW> &su, const SlotStates<Q, CPB, NW> &su0, const SlotResiduals<Q, CPB, NW> &sres) {
   using G = StageGeometry<Q, CPB, NW>;
   G g(p, tid, bid, smem);
   constexpr int F = G::F, FQ = G::FQ;
   if (!g.active) return;
-  const int tile = g.tile, tl = g.tl, lc = g.lc;
-  const double *uin = p.u_in + (size_t)tile * F * kTile + tl;
-  const double *u0p = p.u0 + (size_t)tile * F * kTile + tl;
-  double *out = p.u_out + (size_t)tile * F * kTile + tl;
-  const bool need_u0 = p.mode >= kModeRk3b;
-#pragma unroll 1
+  const int lc = g.lc;
+  double *out = p.u_out + (size_t)g.tile * F * kTile + g.tl;
+  const double dt = p.dt;
+#pragma unroll
   for (int s = 0; s < G::SLOTS; ++s) {
     const int n = g.Node(s);
     if (n < 0) continue;
     const int i0 = n / FQ, i1 = (n / Q) % Q, i2 = n % Q;
-    // issue every global load of this node up front: own state, u0, face descriptors
-    double u[5], u0[5];
+    double r[5];
 #pragma unroll
-    for (int c = 0; c < 5; ++c) u[c] = uin[(n * 5 + c) * kTile];
-#pragma unroll
-    for (int c = 0; c < 5; ++c) u0[c] = need_u0 ? u0p[(n * 5 + c) * kTile] : 0.0;
-    int fq[3], fnb[3], fcode[3];
+    for (int c = 0; c < 5; ++c) r[c] = g.sR[(n * 5 + c) * CPB + lc];
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
       const int id = d == 0 ? i0 : (d == 1 ? i1 : i2);
-      fq[d] = c_tab.node_q[n][d];
-      const bool plus = id != 0;                   // faces 2,3,5 are the +1 sides
-      const int f = (d == 0) ? (plus ? 2 : 4) : (d == 1) ? (plus ? 3 : 1) : (plus ? 5 : 0);
-      fnb[d] = 0; fcode[d] = 0;
-      if (fq[d] >= 0) {
-        fnb[d] = p.nbr[((size_t)tile * 6 + f) * kTile + tl];
-        fcode[d] = p.code[((size_t)tile * 6 + f) * kTile + tl];
-      }
+      const int q = c_tab.node_q[n][d];
+      if (q < 0) continue;
+      const int pt = FaceOf(d, id != 0) * FQ + q;
+#pragma unroll
+      for (int c = 0; c < 5; ++c) r[c] += g.sC[((size_t)pt * 5 + c) * CPB + lc];
     }
-    double vcur[5], vnext[5];
-    GatherNeighbour<F, FQ>(p, g.sNbrNode, fq[0], fnb[0], fcode[0], vcur);
-    // flux divergence along the three node lines (fr/general.hpp:280-286; dg/lobatto.hpp:161-170)
-    double r[5] = {0, 0, 0, 0, 0};
-#pragma unroll
-    for (int d = 0; d < 3; ++d) {
-      const int id = d == 0 ? i0 : (d == 1 ? i1 : i2);
-      const int st = d == 0 ? FQ : (d == 1 ? Q : 1);
-      const int base = n - id * st;
-#pragma unroll
-      for (int mm = 0; mm < Q; ++mm) {
-        const double a = c_tab.a[id][mm];
-        const double *src = g.sF + ((size_t)(base + mm * st) * 15 + d * 5) * CPB + lc;
-#pragma unroll
-        for (int c = 0; c < 5; ++c) r[c] = fma(a, src[c * CPB], r[c]);
-      }
-    }
-    const Metric m = ComputeMetric(g.sG + lc, CPB, c_tab.xi[i0], c_tab.xi[i1], c_tab.xi[i2]);
-    // face corrections (fr/lobatto.hpp:232-251, 278-428; fr/general.hpp:296-315; dg/lobatto.hpp:171-191)
-    // One rolled loop (a single copy of the Riemann solver in the instruction stream); the next
-    // face's neighbour state is requested before the current face is solved.
-#pragma unroll 1
-    for (int d = 0; d < 3; ++d) {
-      const int q = Sel3(d, fq[0], fq[1], fq[2]);
-      const int nb = Sel3(d, fnb[0], fnb[1], fnb[2]);
-      const int code = Sel3(d, fcode[0], fcode[1], fcode[2]);
-      if (d < 2) {
-        GatherNeighbour<F, FQ>(p, g.sNbrNode, Sel3(d + 1, fq[0], fq[1], fq[2]), Sel3(d + 1, fnb[0], fnb[1], fnb[2]),
-            Sel3(d + 1, fcode[0], fcode[1], fcode[2]), vnext);
-      }
-      if (q >= 0) {
-        const int id = Sel3(d, i0, i1, i2);
-        const double sgn = id != 0 ? 1.0 : -1.0;
-        double nx = Sel3(d, m.s[0][0], m.s[1][0], m.s[2][0]);
-        double ny = Sel3(d, m.s[0][1], m.s[1][1], m.s[2][1]);
-        double nz = Sel3(d, m.s[0][2], m.s[1][2], m.s[2][2]);
-        const double area = sqrt(nx * nx + ny * ny + nz * nz);
-        const double inv = sgn / area;
-        nx *= inv; ny *= inv; nz *= inv;           // outward unit normal
-        double fl[5];
-        bool skip = false;
-        if (nb >= 0) {
-          // The Riemann problem is posed in the holder's frame, as the reference does: when the
-          // neighbour holds the face, swap the states, flip the normal and negate the result.
-          const bool holder = (code & 64) != 0;
-          const double hs = holder ? 1.0 : -1.0;
-          double ul[5], ur[5];
-#pragma unroll
-          for (int c = 0; c < 5; ++c) {
-            ul[c] = holder ? u[c] : vcur[c];
-            ur[c] = holder ? vcur[c] : u[c];
-          }
-          FluxUpwind<kRiemann>(ul, ur, hs * nx, hs * ny, hs * nz, fl);
-#pragma unroll
-          for (int c = 0; c < 5; ++c) fl[c] *= hs;
-        } else {
-          const int b = -1 - nb;
-          const int kind = p.bkind[b];
-          skip = kind == kBcNoSlip;
-          if (!skip) {
-            State5 ui, given;
-            const double *gv = p.bvals + ((size_t)b * FQ + q) * 5;
-#pragma unroll
-            for (int c = 0; c < 5; ++c) { ui.v[c] = u[c]; given.v[c] = gv[c]; }
-            const State5 bf = BoundaryFluxOutOfLine<kRiemann>(kind, ui, given, nx, ny, nz);
-#pragma unroll
-            for (int c = 0; c < 5; ++c) fl[c] = bf.v[c];
-          }
-        }
-        if (!skip) {
-          const double cf = c_tab.coef_f * area, cF = c_tab.coef_F * sgn;
-          const double *own = g.sF + ((size_t)n * 15 + d * 5) * CPB + lc;
-#pragma unroll
-          for (int c = 0; c < 5; ++c) r[c] = fma(cF, own[c * CPB], fma(-cf, fl[c], r[c]));
-        }
-      }
-#pragma unroll
-      for (int c = 0; c < 5; ++c) vcur[c] = vnext[c];
-    }
-    const double inv_det = 1.0 / m.det;            // fr/general.hpp:256-266; dg/lobatto.hpp:143-158
-    const double dt = p.dt;
 #pragma unroll
     for (int c = 0; c < 5; ++c) {
-      const double res = r[c] * inv_det;
+      const double u = su.u[s][c], u0 = su0.u[s][c], res = r[c] * sres.inv_det[s];
       double val;
       switch (p.mode) {
       case kModeResidual: val = res; break;
-      case kModeEuler: val = u[c] + res * dt; break;
-      case kModeRk3b: val = (u0[c] * 3 + (u[c] + res * dt)) * 0.25; break;
-      case kModeRk3c: val = ((u[c] + res * dt) * 2 + u0[c]) / 3; break;
-      default: val = ((u[c] + res * dt) + u0[c]) * 0.5; break;
+      case kModeEuler: val = u + res * dt; break;
+      case kModeRk3b: val = (u0 * 3 + (u + res * dt)) * 0.25; break;
+      case kModeRk3c: val = ((u + res * dt) * 2 + u0) / 3; break;
+      default: val = ((u + res * dt) + u0) * 0.5; break;
       }
       out[(n * 5 + c) * kTile] = val;
     }
   }
 }
 
+// One CTA-sized block, all phases; `sync` is __syncthreads() on the device and a no-op marker on the
+// host, where RunStageBlockOnHost() below replays the phases thread by thread.
 #ifdef __CUDACC__
 template <int Q, int kRiemann, int CPB, int NW>
 __global__ void __launch_bounds__(NW * 32, (Q == 3 ? 2 : 1))
 StageKernel(StageArgs p) {
   extern __shared__ double smem[];
-  StagePrologue<Q, CPB, NW>(p, threadIdx.x, blockIdx.x, smem);
+  const int tid = threadIdx.x, bid = blockIdx.x;
+  SlotStates<Q, CPB, NW> su;
+  SlotResiduals<Q, CPB, NW> res;
+  StageLoadSlots<Q, CPB, NW>(p, tid, bid, smem, p.u_in, &su);
+  StagePrologue<Q, CPB, NW>(p, tid, bid, smem);
   __syncthreads();
-  StagePhaseA<Q, CPB, NW>(p, threadIdx.x, blockIdx.x, smem);
+  StagePhaseA<Q, CPB, NW>(p, tid, bid, smem, su, &res);
   __syncthreads();
-  StagePhaseB<Q, kRiemann, CPB, NW>(p, threadIdx.x, blockIdx.x, smem);
+  StagePhaseB1<Q, CPB, NW>(p, tid, bid, smem, &res);
+  __syncthreads();
+  StageStoreResiduals<Q, CPB, NW>(p, tid, bid, smem, res);
+  StagePhaseB2<Q, kRiemann, CPB, NW>(p, tid, bid, smem);
+  // the states needed by the update are requested before the last barrier
+  SlotStates<Q, CPB, NW> su0;
+  StageLoadSlots<Q, CPB, NW>(p, tid, bid, smem, p.u_in, &su);
+  StageLoadSlots<Q, CPB, NW>(p, tid, bid, smem, p.mode >= kModeRk3b ? p.u0 : p.u_in, &su0);
+  __syncthreads();
+  StagePhaseC<Q, CPB, NW>(p, tid, bid, smem, su, su0, res);
 }
+#else
+template <int Q, int kRiemann, int CPB, int NW>
+void RunStageBlockOnHost(const StageArgs &p, int bid, double *smem) {
+  constexpr int T = NW * 32;
+  static SlotStates<Q, CPB, NW> su[T], su0[T];
+  static SlotResiduals<Q, CPB, NW> res[T];
+  for (int t = 0; t < T; ++t) {
+    StageLoadSlots<Q, CPB, NW>(p, t, bid, smem, p.u_in, &su[t]);
+    StagePrologue<Q, CPB, NW>(p, t, bid, smem);
+  }
+  for (int t = 0; t < T; ++t) StagePhaseA<Q, CPB, NW>(p, t, bid, smem, su[t], &res[t]);
+  for (int t = 0; t < T; ++t) StagePhaseB1<Q, CPB, NW>(p, t, bid, smem, &res[t]);
+  for (int t = 0; t < T; ++t) StageStoreResiduals<Q, CPB, NW>(p, t, bid, smem, res[t]);
+  for (int t = 0; t < T; ++t) {
+    StagePhaseB2<Q, kRiemann, CPB, NW>(p, t, bid, smem);
+    StageLoadSlots<Q, CPB, NW>(p, t, bid, smem, p.mode >= kModeRk3b ? p.u0 : p.u_in, &su0[t]);
+  }
+  for (int t = 0; t < T; ++t) StagePhaseC<Q, CPB, NW>(p, t, bid, smem, su[t], su0[t], res[t]);
+}
+#endif
 
+#ifdef __CUDACC__
 // FiniteElement::GetTimeStep's reduction (fem.hpp:417-432; rotated/euler.hpp:340-345): one thread per
 // cell, min over cells of length / max(1e-5, max_nodes(c + |v|)), folded into *result by atomicMin
 // on the bit pattern (valid for non-negative doubles).

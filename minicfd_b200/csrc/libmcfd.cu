@@ -132,8 +132,8 @@ int LaunchStage(mcfd_ctx *ctx, const double *u_in, const double *u0, double *u_o
     ctx->events_used++;
     MCFD_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
   }
-  cudaError_t e = (ctx->q == 3) ? LaunchStageQ<3, 32, 9>(ctx, a, n_blocks)
-                                : LaunchStageQ<4, 16, 16>(ctx, a, n_blocks);
+  cudaError_t e = (ctx->q == 3) ? LaunchStageQ<3, kP2Cells, kP2Warps>(ctx, a, n_blocks)
+                                : LaunchStageQ<4, kP3Cells, kP3Warps>(ctx, a, n_blocks);
   if (e != cudaSuccess) return Fail(ctx, MCFD_ERR_CUDA, std::string("stage kernel: ") + cudaGetErrorString(e));
   if (ctx->timing) MCFD_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
   ctx->launches++;
@@ -231,8 +231,8 @@ int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
   ctx->q = config->degree + 1;
   ctx->n_nodes = ctx->q * ctx->q * ctx->q;
   ctx->fields = 5 * ctx->n_nodes;
-  ctx->cpb = (ctx->q == 3) ? 32 : 16;
-  ctx->n_warps = (ctx->q == 3) ? 9 : 16;
+  ctx->cpb = (ctx->q == 3) ? kP2Cells : kP3Cells;
+  ctx->n_warps = (ctx->q == 3) ? kP2Warps : kP3Warps;
   ctx->tables = BuildTables(config->degree, config->scheme, ctx->n_warps, kTile / ctx->cpb);
   e = cudaMemcpyToSymbol(c_tab, &ctx->tables, sizeof(Tables));
   if (e != cudaSuccess) return Fail(nullptr, MCFD_ERR_CUDA, cudaGetErrorString(e));

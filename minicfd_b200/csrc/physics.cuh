@@ -39,6 +39,41 @@ constexpr double kGammaOverGm1 = kGamma / kGm1;
 
 enum : int { kExact = 0, kHllc = 1, kAusm = 2 };
 
+// Reciprocal, reciprocal square root, square root and quotient to ~1 ulp for NORMAL positive (Rcp:
+// non-zero) arguments: the 20-bit MUFU seed plus two Newton steps in FP64.  The IEEE-exact `/` and
+// sqrt() expand to 20-30 instructions each with special-case branches; a face point needs about a
+// dozen of them, so they dominated the FP64 pipe.  The results differ from the correctly rounded
+// ones by at most a unit in the last place, far inside the 1e-12 parity bound; zero, subnormal,
+// infinite and NaN arguments are the caller's business (every call site guards or cannot see them).
+#ifdef __CUDACC__
+MCFD_HD double Rcp(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  r = fma(r, fma(-x, r, 1.0), r);
+  r = fma(r, fma(-x, r, 1.0), r);
+  return r;
+}
+MCFD_HD double Rsqrt(double x) {
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  double e = fma(-x * y, y, 1.0);
+  y = fma(0.5 * y, e, y);
+  e = fma(-x * y, y, 1.0);
+  y = fma(0.5 * y, e, y);
+  return y;
+}
+MCFD_HD double Sqrt(double x) {
+  const double y = Rsqrt(x);
+  const double s = x * y;
+  return fma(fma(-s, s, x), 0.5 * y, s);
+}
+#else
+MCFD_HD double Rcp(double x) { return 1.0 / x; }
+MCFD_HD double Rsqrt(double x) { return 1.0 / sqrt(x); }
+MCFD_HD double Sqrt(double x) { return sqrt(x); }
+#endif
+MCFD_HD double Div(double a, double b) { return a * Rcp(b); }
+
 // pow() expands to several hundred instructions; one shared copy keeps the stage kernel's hot loop
 // inside the instruction cache.
 MCFD_NOINLINE double Pow(double x, double y) { return pow(x, y); }
@@ -55,7 +90,7 @@ MCFD_HD Prim ConsToPrim(double r, double mx, double my, double mz, double e) {
     return q;
   }
   if (r != 0) {
-    double inv = 1.0 / r;
+    double inv = Rcp(r);
     q.rho = r;
     q.u = mx * inv;
     q.v = my * inv;
@@ -73,7 +108,7 @@ MCFD_HD Prim ConsToPrim(double r, double mx, double my, double mz, double e) {
 
 // IdealGas::GetSpeedOfSound (types.hpp:252-254)
 MCFD_HD double SoundSpeed(double rho, double p) {
-  return (rho > 0 && p > 0) ? sqrt(kGamma * p / rho) : 0.0;
+  return (rho > 0 && p > 0) ? Sqrt(kGamma * Div(p, rho)) : 0.0;
 }
 
 // Result of a 1-D solver in the normal frame: mass, normal momentum and energy flux plus the
@@ -95,7 +130,7 @@ MCFD_HD void StateFlux(double rho, double un, double p, double ke,
 // ---- HLLC (hllc.hpp:30-44, 54-109) -------------------------------------------------------------
 MCFD_HD double HllcQ(double p_est, double p_k) {
   if (p_est <= p_k) return 1.0;
-  return sqrt(1 + kGp1Over2 * (p_est / p_k - 1) / kGamma);
+  return Sqrt(1 + (kGp1Over2 / kGamma) * (Div(p_est, p_k) - 1));
 }
 
 MCFD_HD NormalFlux HllcStar(double rho, double un, double p, double ke,
@@ -103,8 +138,8 @@ MCFD_HD NormalFlux HllcStar(double rho, double un, double p, double ke,
   NormalFlux f;
   StateFlux(rho, un, p, ke, &f.mass, &f.mom_n, &f.energy);
   double energy = p * kOneOverGm1 + rho * ke;
-  double temp = rho * (wave_k - un) / (wave_k - wave_star);
-  double e_star = energy / rho + (wave_star - un) * (wave_star + p / (rho * (wave_k - un)));
+  double temp = rho * Div(wave_k - un, wave_k - wave_star);
+  double e_star = Div(energy, rho) + (wave_star - un) * (wave_star + Div(p, rho * (wave_k - un)));
   e_star *= temp;
   f.mass += (temp - rho) * wave_k;
   f.mom_n += (temp * wave_star - rho * un) * wave_k;
@@ -122,8 +157,8 @@ MCFD_HD NormalFlux SolveHllc(double rl, double ul, double pl, double kel,
   double p_est = fmax(0.0, p_pvrs);
   double wl = ul - al * HllcQ(p_est, pl);
   double wr = ur + ar * HllcQ(p_est, pr);
-  double ws = (pr - pl + rl * ul * (wl - ul) - rr * ur * (wr - ur)) /
-              (rl * (wl - ul) - rr * (wr - ur));
+  double ws = Div(pr - pl + rl * ul * (wl - ul) - rr * ur * (wr - ur),
+                  rl * (wl - ul) - rr * (wr - ur));
   NormalFlux f;
   f.c_left = f.c_right = 0;
   if (0.0 <= wl) {
@@ -147,8 +182,8 @@ template <bool kNegative>
 MCFD_HD void AusmSigned(double rho, double un, double p_in, double ke,
     double *m_out, double *p_out, double *h_out) {
   double a = SoundSpeed(rho, p_in);
-  double h = a * a / kGm1 + ke;
-  double mach = un / a;
+  double h = a * a * kOneOverGm1 + ke;
+  double mach = un / a;  // a may be 0 for a vacuum state: keep the IEEE quotient here
   double p = p_in;
   double signed_mach = (1 + (kNegative ? -mach : mach)) * 0.5;
   if (mach >= -1 && mach <= 1) {

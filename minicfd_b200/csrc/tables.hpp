@@ -109,7 +109,10 @@ inline Tables BuildTables(int degree, int scheme, int n_warps, int sub) {
   int face_node[6][kMaxFaceQ];
   for (int f = 0; f < 6; ++f)
     for (int ia = 0; ia < q; ++ia)
-      for (int ib = 0; ib < q; ++ib) face_node[f][ia * q + ib] = FaceNode(q, x, f, ia, ib);
+      for (int ib = 0; ib < q; ++ib) {
+        face_node[f][ia * q + ib] = FaceNode(q, x, f, ia, ib);
+        t.face_node[f][ia * q + ib] = (unsigned char)face_node[f][ia * q + ib];
+      }
   for (int c = 0; c < n; ++c) {
     int ijk[3] = {c / fq, (c / q) % q, c % q};
     for (int d = 0; d < 3; ++d) {

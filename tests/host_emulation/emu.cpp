@@ -19,11 +19,7 @@ template <int Q, int R, int CPB, int NW>
 void RunStage(StageArgs a, int n_blocks) {
   using G = StageGeometry<Q, CPB, NW>;
   std::vector<double> smem(G::kSharedBytes / sizeof(double) + 1);
-  for (int b = 0; b < n_blocks; ++b) {
-    for (int t = 0; t < NW * 32; ++t) StagePrologue<Q, CPB, NW>(a, t, b, smem.data());
-    for (int t = 0; t < NW * 32; ++t) StagePhaseA<Q, CPB, NW>(a, t, b, smem.data());
-    for (int t = 0; t < NW * 32; ++t) StagePhaseB<Q, R, CPB, NW>(a, t, b, smem.data());
-  }
+  for (int b = 0; b < n_blocks; ++b) RunStageBlockOnHost<Q, R, CPB, NW>(a, b, smem.data());
 }
 
 template <int Q, int CPB, int NW>
@@ -54,7 +50,7 @@ int emu_stage(int degree, int scheme, int riemann, int64_t n_nodes, const double
     const int32_t *tag_kinds, const double *bvals, const double *column_in, const double *column_u0,
     int mode, double dt, double *column_out, char *err, int err_len) {
   const int q = degree + 1, F = 5 * q * q * q;
-  const int cpb = (q == 3) ? 32 : 16, nw = (q == 3) ? 9 : 16;
+  const int cpb = (q == 3) ? kP2Cells : kP3Cells, nw = (q == 3) ? kP2Warps : kP3Warps;
   c_tab = BuildTables(degree, scheme, nw, kTile / cpb);
   HostMesh mesh;
   if (!mesh.Build(degree, n_nodes, xyz, n_local, n_ghost, cell_nodes, n_bfaces, bface_nodes,
@@ -80,8 +76,8 @@ int emu_stage(int degree, int scheme, int riemann, int64_t n_nodes, const double
   a.bkind = bkind.data(); a.bvals = bvals ? bvals : zero_vals.data();
   a.n_local = (int)n_local; a.block_begin = 0; a.mode = mode; a.dt = dt;
   int n_blocks = (int)((n_local + cpb - 1) / cpb);
-  if (q == 3) RunStageQ<3, 32, 9>(riemann, a, n_blocks);
-  else RunStageQ<4, 16, 16>(riemann, a, n_blocks);
+  if (q == 3) RunStageQ<3, kP2Cells, kP2Warps>(riemann, a, n_blocks);
+  else RunStageQ<4, kP3Cells, kP3Warps>(riemann, a, n_blocks);
   for (int64_t c = 0; c < n_local; ++c)
     for (int f = 0; f < F; ++f) column_out[c * F + f] = uout[((c >> 5) * F + f) * kTile + (c & 31)];
   return 0;
@@ -100,7 +96,7 @@ int64_t emu_boundary(int degree, int64_t n_nodes, const double *xyz, int64_t n_l
     tag[b] = mesh.bound_faces[b].tag;
   }
   if (points) {  // [face][Q*Q][3] in boundary-face order (tags ascending)
-    Tables t = BuildTables(degree, 0, degree == 2 ? 9 : 16, degree == 2 ? 1 : 2);
+    Tables t = BuildTables(degree, 0, degree == 2 ? kP2Warps : kP3Warps, kTile / (degree == 2 ? kP2Cells : kP3Cells));
     const int fq = (degree + 1) * (degree + 1);
     int last = -1;
     for (size_t b = 0; b < mesh.bound_faces.size(); ++b) {
