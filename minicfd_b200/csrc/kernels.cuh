@@ -27,9 +27,15 @@ constexpr int kMaxSlots = 8;    // node slots per warp
 constexpr int kMaxWarps = 16;
 // launch shape per degree: cells per CTA and warps per CTA (see StageKernel)
 #ifndef MCFD_P2_WARPS
-#define MCFD_P2_WARPS 8
+#define MCFD_P2_WARPS 10
 #endif
-constexpr int kP2Cells = 32, kP2Warps = MCFD_P2_WARPS, kP3Cells = 16, kP3Warps = 16;
+#ifndef MCFD_P2_CELLS
+#define MCFD_P2_CELLS 32
+#endif
+#ifndef MCFD_P2_MINB
+#define MCFD_P2_MINB 2
+#endif
+constexpr int kP2Cells = MCFD_P2_CELLS, kP2Warps = MCFD_P2_WARPS, kP3Cells = 16, kP3Warps = 16;
 
 // Per-degree tables, filled by the host (tables.cpp) and copied to constant memory.
 struct Tables {
@@ -475,7 +481,7 @@ MCFD_HD void StagePhaseC(const StageArgs &p, int tid, int bid, double *smem,
 // host, where RunStageBlockOnHost() below replays the phases thread by thread.
 #ifdef __CUDACC__
 template <int Q, int kRiemann, int CPB, int NW>
-__global__ void __launch_bounds__(NW * 32, (Q == 3 ? 2 : 1))
+__global__ void __launch_bounds__(NW * 32, (Q == 3 ? MCFD_P2_MINB : 1))
 StageKernel(StageArgs p) {
   extern __shared__ double smem[];
   const int tid = threadIdx.x, bid = blockIdx.x;

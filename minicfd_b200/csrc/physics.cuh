@@ -128,24 +128,9 @@ MCFD_HD void StateFlux(double rho, double un, double p, double ke,
 }
 
 // ---- HLLC (hllc.hpp:30-44, 54-109) -------------------------------------------------------------
-MCFD_HD double HllcQ(double p_est, double p_k) {
+MCFD_HD double HllcQ(double p_est, double p_k) {   // hllc.hpp:69-77
   if (p_est <= p_k) return 1.0;
   return Sqrt(1 + (kGp1Over2 / kGamma) * (Div(p_est, p_k) - 1));
-}
-
-MCFD_HD NormalFlux HllcStar(double rho, double un, double p, double ke,
-    double wave_k, double wave_star) {
-  NormalFlux f;
-  StateFlux(rho, un, p, ke, &f.mass, &f.mom_n, &f.energy);
-  double energy = p * kOneOverGm1 + rho * ke;
-  double temp = rho * Div(wave_k - un, wave_k - wave_star);
-  double e_star = Div(energy, rho) + (wave_star - un) * (wave_star + Div(p, rho * (wave_k - un)));
-  e_star *= temp;
-  f.mass += (temp - rho) * wave_k;
-  f.mom_n += (temp * wave_star - rho * un) * wave_k;
-  f.energy += (e_star - energy) * wave_k;
-  f.c_left = f.c_right = 0;
-  return f;
 }
 
 MCFD_HD NormalFlux SolveHllc(double rl, double ul, double pl, double kel,
@@ -159,21 +144,27 @@ MCFD_HD NormalFlux SolveHllc(double rl, double ul, double pl, double kel,
   double wr = ur + ar * HllcQ(p_est, pr);
   double ws = Div(pr - pl + rl * ul * (wl - ul) - rr * ur * (wr - ur),
                   rl * (wl - ul) - rr * (wr - ur));
+  // The four cases of hllc.hpp:34-43 without divergent control flow: pick the side K whose state
+  // the flux starts from, then add the star-region jump S_K (U*_K - U_K) unless the t-axis lies
+  // outside the fan on that side.
+  const bool left = (0.0 <= wl) || (!(wr <= 0.0) && (0.0 <= ws));
+  const bool star = !(0.0 <= wl) && !(wr <= 0.0);
+  const double rho = left ? rl : rr, un = left ? ul : ur, p = left ? pl : pr, ke = left ? kel : ker;
+  const double wk = left ? wl : wr;
   NormalFlux f;
-  f.c_left = f.c_right = 0;
-  if (0.0 <= wl) {
-    StateFlux(rl, ul, pl, kel, &f.mass, &f.mom_n, &f.energy);
-    f.c_left = f.mass;
-  } else if (wr <= 0.0) {
-    StateFlux(rr, ur, pr, ker, &f.mass, &f.mom_n, &f.energy);
-    f.c_right = f.mass;
-  } else if (0.0 <= ws) {
-    f = HllcStar(rl, ul, pl, kel, wl, ws);
-    f.c_left = f.mass;
-  } else {
-    f = HllcStar(rr, ur, pr, ker, wr, ws);
-    f.c_right = f.mass;
+  StateFlux(rho, un, p, ke, &f.mass, &f.mom_n, &f.energy);
+  if (star) {   // uniform across a warp almost everywhere (subsonic normal velocity)
+    const double energy = p * kOneOverGm1 + rho * ke;
+    const double dk = wk - un;
+    const double temp = rho * Div(dk, wk - ws);
+    double e_star = Div(energy, rho) + (ws - un) * (ws + Div(p, rho * dk));
+    e_star *= temp;
+    f.mass += (temp - rho) * wk;
+    f.mom_n += (temp * ws - rho * un) * wk;
+    f.energy += (e_star - energy) * wk;
   }
+  f.c_left = left ? f.mass : 0.0;
+  f.c_right = left ? 0.0 : f.mass;
   return f;
 }
 
