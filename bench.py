@@ -40,7 +40,7 @@ RIEMANN = {"exact": 0, "hllc": 1, "ausm": 2}
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=400)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cells", type=int, default=42, help="cells per direction per GPU")
@@ -57,42 +57,61 @@ def parse():
 # clocks
 # ---------------------------------------------------------------------------------------------------
 class ClockSampler:
-    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+    """`nvidia-smi -lms` running beside the timed region (B200_PROFILING.md's clocks line); samples
+    taken between mark_begin() and mark_end() are the ones "under load"."""
+    FIELDS = ("timestamp,clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
               "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
               "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index=0):
-        self.index, self.samples, self._stop = index, [], threading.Event()
-        self.thread = threading.Thread(target=self._run, daemon=True)
-
-    def _run(self):
-        while not self._stop.is_set():
-            try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
-                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
-                parts = [p.strip() for p in out.strip().split(",")]
-                if len(parts) >= 6:
-                    self.samples.append(parts)
-            except Exception:
-                pass
-            self._stop.wait(0.1)
+    def __init__(self, index=0, period_ms=20):
+        self.index, self.period_ms, self.proc, self.t0, self.t1 = index, period_ms, None, None, None
 
     def __enter__(self):
-        self.thread.start()
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", str(self.period_ms)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            time.sleep(0.25)   # let it produce its first samples
+        except Exception:
+            self.proc = None
         return self
 
+    def mark_begin(self):
+        self.t0 = time.time()
+
+    def mark_end(self):
+        self.t1 = time.time()
+
     def __exit__(self, *a):
-        self._stop.set()
-        self.thread.join(timeout=6)
+        if self.proc is not None:
+            time.sleep(0.05)
+            self.proc.terminate()
+            try:
+                self.out = self.proc.communicate(timeout=5)[0]
+            except Exception:
+                self.proc.kill()
+                self.out = ""
 
     def summary(self):
-        if not self.samples:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
-        sm = sorted(float(s[0]) for s in self.samples)
+        import datetime
+        rows = []
+        for line in getattr(self, "out", "").splitlines():
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                ts = datetime.datetime.strptime(parts[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                rows.append((ts, float(parts[1]), float(parts[2]), parts[3:7]))
+            except ValueError:
+                continue
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"], "samples": 0}
+        load = [r for r in rows if self.t0 is not None and self.t0 - 0.02 <= r[0] <= self.t1 + 0.02] or rows
+        sm = sorted(r[1] for r in load)
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.samples[0][1]), "reasons": reasons,
-                "samples": len(sm)}
+        reasons = [n for i, n in enumerate(names) if any(r[3][i].lower().startswith("active") for r in load)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": rows[0][2], "reasons": reasons,
+                "samples_under_load": len(load), "samples": len(rows)}
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -240,11 +259,14 @@ def ours(args):
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local_rank) as clocks:
+        barrier()
+        clocks.mark_begin()
         e0.record()
         for _ in range(args.steps):
             t += step_device(t)
         e1.record()
         barrier()
+        clocks.mark_end()
     ms = e0.elapsed_time(e1)
     kernel_ms, kernel_launches = sp.ctx.kernel_time(reset=True)
     sp.ctx.enable_kernel_timing(False)

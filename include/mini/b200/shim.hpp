@@ -1,0 +1,460 @@
+// mini/b200/shim.hpp — header-style C++ host side of the B200 path.
+//
+// Keeps the names, template parameters and member functions that a miniCFD driver uses for the hot
+// path (demo/euler/sourceless.hpp:15-111, demo/euler/sourceless.cpp:107-221 of the reference) and forwards the
+// work to the C ABI of include/minicfd_b200.h.  The classes are thin: geometry, connectivity and the
+// solution live on the GPU; the host keeps the mesh description and the boundary functions.
+//
+//   reference type (include/mini/...)                          here
+//   integrator::Lobatto<S,Q>          integrator/lobatto.hpp:20   tag carrying Q
+//   polynomial::Hexahedron<Gx,Gy,Gz,K,kLocal>  polynomial/hexahedron.hpp:41  tag carrying P, K, N + value types
+//   riemann::euler::IdealGas / Exact / HartenLaxLeerContact / AdvectionUpstreamSplittingMethod
+//                                     riemann/euler/*.hpp         tags + host-side PrimitiveToConservative
+//   riemann::rotated::Euler<U>        riemann/rotated/euler.hpp:23  tag
+//   mesh::part::Part<Int,Poly>        mesh/part.hpp:404           in-memory part (no CGNS/MPI I/O)
+//   spatial::fr::Lobatto / dg::Lobatto  spatial/fr/lobatto.hpp:36, spatial/dg/lobatto.hpp:34   GPU-backed System
+//   temporal::System / Euler / RungeKutta   temporal/ode.hpp:17-134, temporal/rk.hpp:10-57
+#ifndef MINI_B200_SHIM_HPP_
+#define MINI_B200_SHIM_HPP_
+
+#include <algorithm>
+#include <array>
+#include <cmath>
+#include <cstdint>
+#include <functional>
+#include <map>
+#include <stdexcept>
+#include <string>
+#include <unordered_map>
+#include <utility>
+#include <vector>
+
+#include "minicfd_b200.h"
+
+namespace mini {
+
+namespace algebra {
+// Stand-in for Eigen's fixed-size vectors in driver code (value semantics, operator[]).
+template <typename Scalar, int kSize>
+struct Vector : std::array<Scalar, kSize> {
+  Vector() { this->fill(Scalar(0)); }
+  Vector(std::initializer_list<Scalar> il) { this->fill(Scalar(0)); std::copy(il.begin(), il.end(), this->begin()); }
+  static Vector Zero() { return Vector(); }
+};
+// Stand-in for Eigen::Vector<Scalar, Dynamic>: the `Column` of temporal::System (temporal/ode.hpp:19).
+template <typename Scalar>
+struct DynamicVector : std::vector<Scalar> {
+  using std::vector<Scalar>::vector;
+  DynamicVector &operator+=(DynamicVector const &that) {
+    for (size_t i = 0; i < this->size(); ++i) (*this)[i] += that[i];
+    return *this;
+  }
+  DynamicVector &operator*=(Scalar s) { for (auto &x : *this) x *= s; return *this; }
+  DynamicVector &operator/=(Scalar s) { for (auto &x : *this) x /= s; return *this; }
+  Scalar squaredNorm() const { Scalar n = 0; for (auto x : *this) n += x * x; return n; }
+  void setZero() { std::fill(this->begin(), this->end(), Scalar(0)); }
+};
+}  // namespace algebra
+
+namespace integrator {
+template <typename S, int N>
+struct Lobatto {  // integrator/lobatto.hpp:20-93
+  using Scalar = S;
+  static constexpr int Q = N;
+  static std::array<S, N> BuildPoints() {
+    if constexpr (N == 3) return {-1.0, 0.0, 1.0};
+    else return {-1.0, -std::sqrt(1.0 / 5), std::sqrt(1.0 / 5), 1.0};
+  }
+};
+}  // namespace integrator
+
+namespace polynomial {
+template <class Gx, class Gy, class Gz, int kComponents, bool kL = false>
+struct Hexahedron {  // polynomial/hexahedron.hpp:41-65
+  static_assert(Gx::Q == Gy::Q && Gy::Q == Gz::Q, "the B200 path needs the same rule in all directions");
+  static_assert(Gx::Q == 3 || Gx::Q == 4, "degree 2 or 3");
+  static_assert(!kL, "kLocal = true (laminar demos) is not built yet");
+  using Scalar = typename Gx::Scalar;
+  using IntegratorX = Gx;
+  static constexpr bool kLocal = kL;
+  static constexpr int P = Gx::Q - 1;
+  static constexpr int N = Gx::Q * Gx::Q * Gx::Q;
+  static constexpr int K = kComponents;
+  static constexpr int D = 3;
+  static constexpr int kFields = K * N;
+  using Global = algebra::Vector<Scalar, 3>;
+  using Local = Global;
+  using Value = algebra::Vector<Scalar, K>;
+};
+}  // namespace polynomial
+
+namespace riemann {
+namespace euler {
+template <typename S, int kDimensions>
+struct Primitives : algebra::Vector<S, kDimensions + 2> {  // types.hpp:114-173
+  using algebra::Vector<S, kDimensions + 2>::Vector;
+  S &rho() { return (*this)[0]; }
+  S &u() { return (*this)[1]; }
+  S &v() { return (*this)[2]; }
+  S &w() { return (*this)[3]; }
+  S &p() { return (*this)[kDimensions + 1]; }
+  S rho() const { return (*this)[0]; }
+  S u() const { return (*this)[1]; }
+  S v() const { return (*this)[2]; }
+  S w() const { return (*this)[3]; }
+  S p() const { return (*this)[kDimensions + 1]; }
+};
+template <typename S, int kDimensions>
+struct Conservatives : algebra::Vector<S, kDimensions + 2> {  // types.hpp:175-184
+  using algebra::Vector<S, kDimensions + 2>::Vector;
+};
+template <typename S, int kGammaTimes10>
+struct IdealGasTag {
+  using Scalar = S;
+  static_assert(kGammaTimes10 == 14, "gamma = 1.4 (demo/euler/sourceless.hpp:21)");
+  static constexpr S Gamma() { return 1.4; }
+  static constexpr S R() { return 287.05; }
+  // types.hpp:302-311
+  static Conservatives<S, 3> PrimitiveToConservative(Primitives<S, 3> const &q) {
+    Conservatives<S, 3> c;
+    c[0] = q.rho(); c[1] = q.rho() * q.u(); c[2] = q.rho() * q.v(); c[3] = q.rho() * q.w();
+    c[4] = q.p() * (1 / (Gamma() - 1)) + q.rho() * (0.5 * (q.u() * q.u() + q.v() * q.v() + q.w() * q.w()));
+    return c;
+  }
+};
+// The reference spells IdealGas<Scalar, 1.4> with a floating-point non-type parameter (C++20).
+template <typename S, double kGamma>
+using IdealGas = IdealGasTag<S, static_cast<int>(kGamma * 10 + 0.5)>;
+
+template <class G, int D> struct Exact { using Gas = G; static constexpr int kKind = MCFD_EXACT; };
+template <class G, int D> struct HartenLaxLeerContact { using Gas = G; static constexpr int kKind = MCFD_HLLC; };
+template <class G, int D> struct AdvectionUpstreamSplittingMethod { using Gas = G; static constexpr int kKind = MCFD_AUSM; };
+}  // namespace euler
+
+namespace rotated {
+template <class Unrotated>
+struct Euler {  // rotated/euler.hpp:23-40
+  using Gas = typename Unrotated::Gas;
+  using Scalar = typename Gas::Scalar;
+  using Convection = Euler;
+  static constexpr int kComponents = 5;
+  static constexpr int kDimensions = 3;
+  static constexpr int kKind = Unrotated::kKind;
+  using Conservative = euler::Conservatives<Scalar, 3>;
+  using Primitive = euler::Primitives<Scalar, 3>;
+  using Value = algebra::Vector<Scalar, 5>;
+};
+}  // namespace rotated
+}  // namespace riemann
+
+namespace b200 {
+inline void Check(int status, mcfd_ctx *ctx, const char *what) {
+  if (status != 0) {
+    throw std::runtime_error(std::string(what) + ": " + mcfd_last_error(ctx));
+  }
+}
+}  // namespace b200
+
+namespace mesh {
+namespace part {
+
+// In-memory part.  The reference constructs a Part from `<case>/shuffled.cgns` + `partition/<rank>.txt`
+// (part.hpp:442-476); that I/O needs CGNS + MPI and stays out of scope, so the mesh is
+// handed over as arrays, already numbered the way part.hpp:746-775 numbers it: local cells (inner
+// first, then inter), then ghost cells.
+template <typename Int, class Poly>
+class Part {
+ public:
+  using Index = Int;
+  using Polynomial = Poly;
+  using Scalar = typename Poly::Scalar;
+  using Global = typename Poly::Global;
+  using Value = typename Poly::Value;
+  static constexpr int kDegrees = Poly::P;
+  static constexpr int kComponents = Poly::K;
+  static constexpr int kFields = Poly::kFields;
+
+  struct Halo {
+    std::vector<int64_t> parts, send_counts, send_cells, recv_counts, recv_cells;
+  };
+
+  Part(int rank, int size) : rank_(rank), size_(size) {}
+
+  // nodes [n_nodes][3]; cell_nodes [n_local + n_ghost][8] (CGNS HEXA_8); boundary quads with the
+  // name of their section (the BC names of the drivers, e.g. "Left", demo/euler/shock_tube.cpp:56-66).
+  void SetMesh(std::vector<Scalar> nodes, std::vector<int64_t> cell_nodes, Int n_local, Int n_ghost,
+      std::vector<int64_t> bface_nodes, std::vector<std::string> const &bface_names, Halo halo = Halo()) {
+    nodes_ = std::move(nodes); cell_nodes_ = std::move(cell_nodes);
+    n_local_ = n_local; n_ghost_ = n_ghost; bface_nodes_ = std::move(bface_nodes); halo_ = std::move(halo);
+    bface_tags_.clear();
+    for (auto const &name : bface_names) {
+      auto it = name_to_tag_.find(name);
+      if (it == name_to_tag_.end()) it = name_to_tag_.emplace(name, (int32_t)name_to_tag_.size()).first;
+      bface_tags_.push_back(it->second);
+    }
+  }
+  int mpi_rank() const { return rank_; }
+  int mpi_size() const { return size_; }
+  Int CountLocalCells() const { return n_local_; }                     // part.hpp:651-658
+  Int CountGhostCells() const { return n_ghost_; }
+  Int GetCellDataOffset(Int i_cell) const { return i_cell * kFields; }  // part.hpp:784-787
+  Int GetCellDataSize() const { return n_local_ * kFields; }            // part.hpp:793-797
+  bool IsLocal(Int i_cell) const { return 0 <= i_cell && i_cell < n_local_; }
+  int32_t TagOf(std::string const &name) const {
+    auto it = name_to_tag_.find(name);
+    if (it == name_to_tag_.end()) throw std::runtime_error("no boundary section named " + name);
+    return it->second;
+  }
+  // Global coordinates of the solution points of a local cell (integrator/hexahedron.hpp:66-80).
+  Global NodeCoordinate(Int i_cell, int ijk) const {
+    auto x = Poly::IntegratorX::BuildPoints();
+    constexpr int Q = Poly::IntegratorX::Q;
+    static const int v[8][3] = {{-1, -1, -1}, {1, -1, -1}, {1, 1, -1}, {-1, 1, -1},
+                                {-1, -1, 1}, {1, -1, 1}, {1, 1, 1}, {-1, 1, 1}};
+    Scalar loc[3] = {x[ijk / (Q * Q)], x[(ijk / Q) % Q], x[ijk % Q]};
+    Global g;
+    for (int c = 0; c < 8; ++c) {
+      Scalar s = (1 + v[c][0] * loc[0]) * (1 + v[c][1] * loc[1]) * (1 + v[c][2] * loc[2]) / 8;
+      for (int d = 0; d < 3; ++d) g[d] += s * nodes_[cell_nodes_[i_cell * 8 + c] * 3 + d];
+    }
+    return g;
+  }
+
+  std::vector<Scalar> nodes_;
+  std::vector<int64_t> cell_nodes_, bface_nodes_;
+  std::vector<int32_t> bface_tags_;
+  std::unordered_map<std::string, int32_t> name_to_tag_;
+  Halo halo_;
+  Int n_local_ = 0, n_ghost_ = 0;
+
+ private:
+  int rank_, size_;
+};
+
+}  // namespace part
+}  // namespace mesh
+
+namespace temporal {
+
+template <typename Scalar>
+class System {  // temporal/ode.hpp:17-48
+ public:
+  using Column = algebra::DynamicVector<Scalar>;
+  virtual ~System() = default;
+  virtual void SetTime(double t_curr) = 0;
+  virtual void SetSolutionColumn(Column const &column) = 0;
+  virtual Column GetSolutionColumn() const = 0;
+  virtual Column GetResidualColumn() const = 0;
+  // GPU-backed systems advance a whole RungeKutta<order>::Update with fused stage kernels.
+  virtual bool FusedUpdate(int order, double t_curr, double dt) { return false; }
+};
+
+template <typename Scalar>
+class Solver {  // temporal/ode.hpp:92-105
+ public:
+  using Column = typename System<Scalar>::Column;
+  virtual ~Solver() = default;
+  virtual void Update(System<Scalar> *ode, double t_curr, double dt) = 0;
+};
+
+template <typename Scalar>
+class Euler : public Solver<Scalar> {  // temporal/ode.hpp:112-134
+ public:
+  using Column = typename Solver<Scalar>::Column;
+  static Column NextSolution(System<Scalar> *system, double t_curr, double dt) {
+    system->SetTime(t_curr);
+    auto u_next = system->GetSolutionColumn();
+    auto residual = system->GetResidualColumn();
+    residual *= dt;
+    u_next += residual;
+    return u_next;
+  }
+  void Update(System<Scalar> *system, double t_curr, double dt) final {
+    if (system->FusedUpdate(1, t_curr, dt)) return;
+    system->SetSolutionColumn(NextSolution(system, t_curr, dt));
+  }
+};
+
+template <int kOrders, typename Scalar>
+struct RungeKutta : public Solver<Scalar> {  // temporal/rk.hpp:10-57
+  static_assert(1 <= kOrders && kOrders <= 3);
+  using Column = typename Solver<Scalar>::Column;
+  void Update(System<Scalar> *system, double t_curr, double dt) final {
+    if (system->FusedUpdate(kOrders, t_curr, dt)) return;   // one fused kernel per stage
+    UpdateGeneric(system, t_curr, dt);
+  }
+  // The reference's column algebra, through the System interface (every residual still on the GPU).
+  void UpdateGeneric(System<Scalar> *system, double t_curr, double dt) {
+    Euler<Scalar> euler;
+    if constexpr (kOrders == 1) {
+      system->SetSolutionColumn(euler.NextSolution(system, t_curr, dt));
+    } else if constexpr (kOrders == 2) {
+      auto u_curr = system->GetSolutionColumn();
+      system->SetSolutionColumn(euler.NextSolution(system, t_curr, dt));
+      auto u_next = euler.NextSolution(system, t_curr + dt, dt);
+      u_next += u_curr;
+      u_next *= 0.5;
+      system->SetSolutionColumn(u_next);
+    } else {
+      auto u_curr = system->GetSolutionColumn();
+      system->SetSolutionColumn(euler.NextSolution(system, t_curr, dt));
+      auto u_next = u_curr;
+      u_next *= 3;
+      u_next += euler.NextSolution(system, t_curr + dt, dt);
+      u_next /= 4;
+      system->SetSolutionColumn(u_next);
+      u_next = euler.NextSolution(system, t_curr + dt / 2, dt);
+      u_next *= 2;
+      u_next += u_curr;
+      u_next /= 3;
+      system->SetSolutionColumn(u_next);
+    }
+  }
+};
+
+}  // namespace temporal
+
+namespace spatial {
+
+// Common GPU-backed implementation of FiniteElement (spatial/fem.hpp:47-436) for the nodal schemes.
+template <class P, class R, int kScheme>
+class FiniteElementB200 : public temporal::System<typename P::Scalar> {
+ public:
+  using Part = P;
+  using Riemann = R;
+  using Scalar = typename Part::Scalar;
+  using Global = typename Part::Global;
+  using Value = typename Part::Value;
+  using Column = typename temporal::System<Scalar>::Column;
+  using Function = std::function<Value(const Global &, double)>;  // fem.hpp:72
+
+  explicit FiniteElementB200(Part *part_ptr, int device = -1) : part_ptr_(part_ptr) {
+    mcfd_config cfg{kScheme, Part::kDegrees, Riemann::kKind, device};
+    if (mcfd_create(&cfg, &ctx_) != 0) throw std::runtime_error(std::string("mcfd_create: ") + mcfd_last_error(nullptr));
+    auto &p = *part_ptr_;
+    b200::Check(mcfd_set_mesh(ctx_, (int64_t)p.nodes_.size() / 3, p.nodes_.data(), p.n_local_, p.n_ghost_,
+        p.cell_nodes_.data(), (int64_t)p.bface_tags_.size(), p.bface_nodes_.data(), p.bface_tags_.data(), 0, nullptr),
+        ctx_, "mcfd_set_mesh");
+    if (p.n_ghost_ > 0) {
+      auto &h = p.halo_;
+      b200::Check(mcfd_set_halo(ctx_, (int32_t)h.send_counts.size(), h.send_counts.data(), h.send_cells.data(),
+          (int32_t)h.recv_counts.size(), h.recv_counts.data(), h.recv_cells.data()), ctx_, "mcfd_set_halo");
+    }
+    b200::Check(mcfd_set_time_callback(ctx_, &FiniteElementB200::OnTime, this), ctx_, "mcfd_set_time_callback");
+  }
+  FiniteElementB200(const FiniteElementB200 &) = delete;
+  FiniteElementB200 &operator=(const FiniteElementB200 &) = delete;
+  ~FiniteElementB200() noexcept override { mcfd_destroy(ctx_); }
+
+  Part *part_ptr() const { return part_ptr_; }
+  Part const &part() const { return *part_ptr_; }
+  mcfd_ctx *context() const { return ctx_; }
+
+  template <class Callable>
+  void Approximate(Callable &&func) {  // fem.hpp:147-154
+    Column column(part().GetCellDataSize());
+    constexpr int N = Part::Polynomial::N, K = Part::kComponents;
+    for (typename Part::Index c = 0; c < part().CountLocalCells(); ++c) {
+      for (int q = 0; q < N; ++q) {
+        Value v = func(part().NodeCoordinate(c, q));
+        for (int k = 0; k < K; ++k) column[(c * N + q) * K + k] = v[k];
+      }
+    }
+    SetSolutionColumn(column);
+  }
+
+  // fem.hpp:196-222
+  template <typename F> void SetSmartBoundary(const std::string &name, F &&f) { SetBc(name, MCFD_BC_SMART, f); }
+  template <typename F> void SetSupersonicInlet(const std::string &name, F &&f) { SetBc(name, MCFD_BC_SUPERSONIC_INLET, f); }
+  template <typename F> void SetSubsonicInlet(const std::string &name, F &&f) { SetBc(name, MCFD_BC_SUBSONIC_INLET, f); }
+  template <typename F> void SetSubsonicOutlet(const std::string &name, F &&f) { SetBc(name, MCFD_BC_SUBSONIC_OUTLET, f); }
+  template <typename F> void SetNoSlipWall(const std::string &name, F &&) { SetBc(name, MCFD_BC_NO_SLIP_WALL, Function()); }
+  void SetInviscidWall(const std::string &name) { SetBc(name, MCFD_BC_INVISCID_WALL, Function()); }
+  void SetSupersonicOutlet(const std::string &name) { SetBc(name, MCFD_BC_SUPERSONIC_OUTLET, Function()); }
+
+  // temporal::System (fem.hpp:225-258)
+  void SetTime(double t_curr) override { t_curr_ = t_curr; }
+  void SetSolutionColumn(Column const &column) override {
+    b200::Check(mcfd_set_solution(ctx_, column.data()), ctx_, "mcfd_set_solution");
+  }
+  Column GetSolutionColumn() const override {
+    Column column(part().GetCellDataSize());
+    b200::Check(mcfd_get_solution(ctx_, column.data()), ctx_, "mcfd_get_solution");
+    return column;
+  }
+  Column GetResidualColumn() const override {
+    Column column(part().GetCellDataSize());
+    b200::Check(mcfd_residual(ctx_, t_curr_, column.data(), nullptr), ctx_, "mcfd_residual");
+    return column;
+  }
+  bool FusedUpdate(int order, double t_curr, double dt) override {
+    if (part().CountGhostCells() > 0) return false;   // parts with ghosts are driven stage by stage
+    b200::Check(mcfd_rk_step(ctx_, order, t_curr, dt), ctx_, "mcfd_rk_step");
+    return true;
+  }
+  Scalar GetTimeStep(Scalar dt_guess, int rk_order) const {  // fem.hpp:417-435, fr/lobatto.hpp:220-222
+    double dt = 0;
+    b200::Check(mcfd_time_step(ctx_, dt_guess, rk_order, &dt), ctx_, "mcfd_time_step");
+    return dt;
+  }
+
+ private:
+  struct Bc { Function func; std::vector<double> points, values; };
+  void SetBc(const std::string &name, int kind, Function func) {
+    int32_t tag = part().TagOf(name);
+    b200::Check(mcfd_set_boundary(ctx_, tag, kind), ctx_, "mcfd_set_boundary");
+    if (!func) return;
+    Bc &bc = bcs_[tag];
+    bc.func = std::move(func);
+    constexpr int fq = (Part::kDegrees + 1) * (Part::kDegrees + 1);
+    int64_t n = mcfd_count_boundary_faces(ctx_, tag);
+    bc.points.resize(n * fq * 3);
+    bc.values.resize(n * fq * 5);
+    if (n) b200::Check(mcfd_get_boundary_points(ctx_, tag, bc.points.data()), ctx_, "mcfd_get_boundary_points");
+    Sample(tag, t_curr_);
+  }
+  // the reference evaluates func(integrator.GetGlobal(f), t_curr_) inside the face loop
+  // (fr/lobatto.hpp:350); here the values are sampled once per residual evaluation and uploaded
+  void Sample(int32_t tag, double t) {
+    Bc &bc = bcs_[tag];
+    size_t n = bc.points.size() / 3;
+    for (size_t i = 0; i < n; ++i) {
+      Global x;
+      for (int d = 0; d < 3; ++d) x[d] = bc.points[i * 3 + d];
+      Value v = bc.func(x, t);
+      for (int k = 0; k < 5; ++k) bc.values[i * 5 + k] = v[k];
+    }
+    if (n) b200::Check(mcfd_set_boundary_values(ctx_, tag, bc.values.data()), ctx_, "mcfd_set_boundary_values");
+  }
+  static void OnTime(void *self, double t) {
+    auto *fe = static_cast<FiniteElementB200 *>(self);
+    for (auto &kv : fe->bcs_) fe->Sample(kv.first, t);
+  }
+
+  Part *part_ptr_;
+  mcfd_ctx *ctx_ = nullptr;
+  double t_curr_ = 0;
+  std::map<int32_t, Bc> bcs_;
+};
+
+namespace fr {
+template <typename P, typename R>
+class Lobatto : public FiniteElementB200<P, R, MCFD_FR_LOBATTO> {  // spatial/fr/lobatto.hpp:36-434
+ public:
+  using FiniteElementB200<P, R, MCFD_FR_LOBATTO>::FiniteElementB200;
+  std::string name() const { return "FR::Lobatto"; }
+};
+}  // namespace fr
+namespace dg {
+template <typename P, typename R>
+class Lobatto : public FiniteElementB200<P, R, MCFD_DG_LOBATTO> {  // spatial/dg/lobatto.hpp:32-303
+ public:
+  using FiniteElementB200<P, R, MCFD_DG_LOBATTO>::FiniteElementB200;
+  std::string name() const { return "DG::Lobatto"; }
+};
+}  // namespace dg
+
+}  // namespace spatial
+}  // namespace mini
+
+#endif  // MINI_B200_SHIM_HPP_
