@@ -169,6 +169,24 @@ double mcfd_rk_stage_time(const mcfd_ctx *ctx, int stage);
  * (demo/euler/sourceless.cpp:191-194). */
 int mcfd_time_step(mcfd_ctx *ctx, double dt_guess, int rk_order, double *dt_local);
 
+/* The same time step as mcfd_time_step, for callers that may not allocate device memory while they run
+ * (a host that gave the whole GPU to its own memory pool, a rank held to a fixed memory budget, a time
+ * loop that must not meet the device-wide synchronisation hidden in cudaMalloc/cudaFree).  No counterpart
+ * in the reference: its GetTimeStep (fem.hpp:417-435) runs on host memory it already owns.
+ * It needs no context and calls no allocator of any kind: inputs and output are the caller's device memory —
+ * column_dev: the solution column [n_cells][N][5] (reference layout); length_dev: Cell::length() of
+ * each cell (mcfd_get_cell_geometry); dt_dev: one double receiving the part-local time step.  The
+ * reduction's scratch is a fixed 1 MiB array inside the library image, held by every GPU that loads
+ * the library until the process ends; it limits a call to 1 048 576 cells and larger n_cells are refused
+ * with MCFD_ERR_ARG (message via mcfd_last_error(NULL)).  The first call on each device looks up the
+ * array's device address (a cudaGetSymbolAddress, no allocation) with that device current: make that
+ * first call outside any stream capture.  All calls share the array: nothing in it has to be cleared
+ * beforehand (every entry a call reads it has written first), but two calls that overlap on the same GPU
+ * (different streams or threads) race on it — serialise them.  Asynchronous on cuda_stream. */
+int mcfd_time_step_static(int32_t scheme, int32_t degree, int64_t n_cells, const double *column_dev,
+                          const double *length_dev, double dt_guess, int32_t rk_order, double *dt_dev,
+                          void *cuda_stream);
+
 /* -- diagnostics --------------------------------------------------------------------------------- */
 
 /* Number of kernels this context has launched so far (bench.py's gpu_launches). */

@@ -64,6 +64,7 @@ SYMBOLS = {
     "mcfd_rk_stage_inter": (C.c_int, [_P, C.c_int]),
     "mcfd_rk_stage_time": (C.c_double, [_P, C.c_int]),
     "mcfd_time_step": (C.c_int, [_P, C.c_double, C.c_int, _D]),
+    "mcfd_time_step_static": (C.c_int, [C.c_int32, C.c_int32, C.c_int64, _P, _P, C.c_double, C.c_int32, _P, _P]),
     "mcfd_launch_count": (C.c_int64, [_P]),
     "mcfd_enable_kernel_timing": (C.c_int, [_P, C.c_int]),
     "mcfd_kernel_time": (C.c_int, [_P, _D, _I64, C.c_int]),
@@ -97,6 +98,16 @@ def _ip(a):
 
 def _i32(a):
     return None if a is None else a.ctypes.data_as(_I32)
+
+
+def time_step_static(scheme, degree, n_cells, column_ptr, length_ptr, dt_guess, rk_order, dt_ptr, stream=0):
+    """mcfd_time_step_static: the time step from caller-owned device buffers, without any allocation
+    (fixed 1 MiB scratch inside the library, at most 1 048 576 cells).  All pointers are device addresses."""
+    lib = load()
+    rc = lib.mcfd_time_step_static(scheme, degree, n_cells, _P(column_ptr), _P(length_ptr), dt_guess, rk_order,
+                                   _P(dt_ptr), _P(stream))
+    if rc != 0:
+        raise McfdError(f"libminicfd_b200 error {rc}: {lib.mcfd_last_error(None).decode()}")
 
 
 class Context:

@@ -639,4 +639,122 @@ int mcfd_riemann_flux(mcfd_ctx *ctx, int32_t bc_kind, int64_t n, const double *n
   return MCFD_OK;
 }
 
+
+// ---- time step without any allocation -------------------------------------------------------------
+//
+// Some hosts of this library must not allocate device memory once they are running: a solver that has
+// handed the whole GPU to its own pool at start-up (a later cudaMalloc would fail or fragment that
+// pool), a rank that runs under a fixed memory budget checked by its job manager, or a time loop whose
+// iterations must not hit the implicit device synchronisation that cudaMalloc/cudaFree carry.
+// mcfd_time_step() needs a context, and contexts allocate.  This entry point needs neither: the caller
+// passes the solution column, the cell lengths and the output, all already on the device, and the
+// reduction's scratch — one partial minimum per block — lives in a fixed array that is part of the
+// library image.  Every GPU that loads the library holds that 1 MiB until the process exits.
+}  // extern "C"
+
+namespace {
+
+constexpr int kStaticCellsPerBlock = 8;                   // one warp per cell
+constexpr int64_t kStaticMaxCells = 1 << 20;              // 1 048 576 cells (141 M DOF at degree 2)
+constexpr int kStaticMaxBlocks = (int)(kStaticMaxCells / kStaticCellsPerBlock);
+
+static __device__ __align__(256) double g_static_dt_partials[kStaticMaxBlocks];   // 1 MiB
+
+// Variant of TimeStepKernel for the reference's column layout [cell][node][component]: a warp takes one
+// cell (lanes over its nodes), a block leaves min(length / max speed) of its 8 cells in partials[block].
+template <int Q>
+__global__ void TimeStepPartialsKernel(const double *column, const double *length, int n_cells,
+    double *partials) {
+  constexpr int N = Q * Q * Q;
+  __shared__ double block_dt[kStaticCellsPerBlock];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cell = blockIdx.x * kStaticCellsPerBlock + warp;
+  double dt = 1e100;
+  if (cell < n_cells) {
+    double vmax = 1e-5;
+    for (int n = lane; n < N; n += 32) {
+      const double *u = column + ((size_t)cell * N + n) * 5;
+      Prim q = ConsToPrim(u[0], u[1], u[2], u[3], u[4]);
+      double c = SoundSpeed(q.rho, q.p);
+      double v = sqrt(q.u * q.u + q.v * q.v + q.w * q.w);
+      vmax = fmax(vmax, fmax(c + v, c - v));
+    }
+    for (int o = 16; o > 0; o >>= 1) vmax = fmax(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+    dt = length[cell] / vmax;
+  }
+  if (lane == 0) block_dt[warp] = dt;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < kStaticCellsPerBlock; ++w) dt = fmin(dt, block_dt[w]);
+    partials[blockIdx.x] = dt;
+  }
+}
+
+// One block folds the partial minima and applies fem.hpp:433-434 and fr/lobatto.hpp:220-222.
+__global__ void TimeStepFinalKernel(const double *partials, int n_partials, double cfl, double dt_guess,
+    int fr_doubling, double *dt_out) {
+  __shared__ double s[1024];
+  double m = 1e100;
+  for (int i = threadIdx.x; i < n_partials; i += blockDim.x) m = fmin(m, partials[i]);
+  s[threadIdx.x] = m;
+  __syncthreads();
+  for (int o = blockDim.x / 2; o > 0; o >>= 1) {
+    if (threadIdx.x < o) s[threadIdx.x] = fmin(s[threadIdx.x], s[threadIdx.x + o]);
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    double dt = fmin(cfl * s[0], dt_guess);
+    if (fr_doubling) dt = fmin(dt_guess, 2.0 * dt);
+    *dt_out = dt;
+  }
+}
+
+// In host code the array's name is only a handle for the runtime, not a device address; the address
+// that kernels can use is looked up once per device, with that device current.
+constexpr int kMaxDevices = 64;
+double *g_static_dt_address[kMaxDevices] = {nullptr};
+
+}  // namespace
+
+extern "C" {
+
+int mcfd_time_step_static(int32_t scheme, int32_t degree, int64_t n_cells, const double *column_dev,
+    const double *length_dev, double dt_guess, int32_t rk_order, double *dt_dev, void *cuda_stream) {
+  if (!column_dev || !length_dev || !dt_dev) return Fail(nullptr, MCFD_ERR_ARG, "mcfd_time_step_static: null pointer");
+  if ((degree != 2 && degree != 3) || (scheme != MCFD_FR_LOBATTO && scheme != MCFD_DG_LOBATTO) || rk_order < 0 || rk_order > 4)
+    return Fail(nullptr, MCFD_ERR_ARG, "mcfd_time_step_static: unsupported scheme, degree or RK order");
+  if (n_cells <= 0) return Fail(nullptr, MCFD_ERR_ARG, "mcfd_time_step_static: n_cells must be positive");
+  if (n_cells > kStaticMaxCells)
+    return Fail(nullptr, MCFD_ERR_ARG, "mcfd_time_step_static: n_cells = " + std::to_string(n_cells) +
+        " exceeds the fixed scratch of " + std::to_string(kStaticMaxCells) +
+        " cells; use mcfd_time_step (which allocates) for larger parts");
+  int device = -1;
+  cudaError_t e = cudaGetDevice(&device);
+  if (e != cudaSuccess) return Fail(nullptr, MCFD_ERR_CUDA, std::string("mcfd_time_step_static: ") + cudaGetErrorString(e));
+  if (device < 0 || device >= kMaxDevices) return Fail(nullptr, MCFD_ERR_ARG, "mcfd_time_step_static: device ordinal out of range");
+  if (!g_static_dt_address[device]) {   // first call on this device
+    double *address = nullptr;
+    e = cudaGetSymbolAddress((void **)&address, g_static_dt_partials);
+    if (e != cudaSuccess || !address)
+      return Fail(nullptr, MCFD_ERR_CUDA, std::string("mcfd_time_step_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+    g_static_dt_address[device] = address;
+  }
+  double *partials = g_static_dt_address[device];
+  static const double cfl[5][9] = {   // fem.hpp:26-37
+    {1.000}, {1.000, 0.333}, {1.000, 0.333, 0.209, 0.130, 0.089, 0.066, 0.051, 0.040, 0.033},
+    {1.256, 0.409, 0.209, 0.130, 0.089, 0.066, 0.051, 0.040, 0.033},
+    {1.392, 0.464, 0.235, 0.145, 0.100, 0.073, 0.056, 0.045, 0.037}};
+  cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+  const int n_blocks = (int)((n_cells + kStaticCellsPerBlock - 1) / kStaticCellsPerBlock);
+  if (degree == 2)
+    TimeStepPartialsKernel<3><<<n_blocks, kStaticCellsPerBlock * 32, 0, stream>>>(column_dev, length_dev, (int)n_cells, partials);
+  else
+    TimeStepPartialsKernel<4><<<n_blocks, kStaticCellsPerBlock * 32, 0, stream>>>(column_dev, length_dev, (int)n_cells, partials);
+  TimeStepFinalKernel<<<1, 1024, 0, stream>>>(partials, n_blocks, cfl[rk_order][degree], dt_guess,
+      scheme == MCFD_FR_LOBATTO, dt_dev);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return Fail(nullptr, MCFD_ERR_CUDA, std::string("mcfd_time_step_static: ") + cudaGetErrorString(e));
+  return MCFD_OK;
+}
+
 }  // extern "C"
