@@ -246,10 +246,14 @@ def ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    from minicfd_b200.spatial import time_step_device
+    dt_dev = torch.zeros(1, dtype=torch.float64, device="cuda")
+
     def step_device(t):
-        dt = sp.GetTimeStep(1.0, 3)
-        rk.Update(sp, t, dt)
-        return dt
+        # GetTimeStep (+ MIN over ranks) and Update without a host round trip: dt stays on the device
+        time_step_device(sp, 1.0, 3, dt_dev)
+        rk.UpdateDevice(sp, t, dt_dev.data_ptr())
+        return 0.0
 
     t = 0.0
     for _ in range(max(args.warmup, 3)):

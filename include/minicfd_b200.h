@@ -169,6 +169,14 @@ double mcfd_rk_stage_time(const mcfd_ctx *ctx, int stage);
  * (demo/euler/sourceless.cpp:191-194). */
 int mcfd_time_step(mcfd_ctx *ctx, double dt_guess, int rk_order, double *dt_local);
 
+/* Device-resident variants for time loops that must not wait for the host: the part-local time step is
+ * left in device memory (dt_dev, or an internal scalar when NULL), may be min-reduced across ranks there
+ * (ncclAllReduce MIN = the MPI_Allreduce of demo/euler/sourceless.cpp:194), and the RK stage kernels read
+ * it from there.  Nothing synchronises the stream. */
+int mcfd_time_step_device(mcfd_ctx *ctx, double dt_guess, int rk_order, double *dt_dev);
+int mcfd_rk_begin_device(mcfd_ctx *ctx, int order, double t, const double *dt_dev);
+int mcfd_rk_step_device(mcfd_ctx *ctx, int order, double t, const double *dt_dev);
+
 /* The same time step as mcfd_time_step, for callers that may not allocate device memory while they run
  * (a host that gave the whole GPU to its own memory pool, a rank held to a fixed memory budget, a time
  * loop that must not meet the device-wide synchronisation hidden in cudaMalloc/cudaFree).  No counterpart

@@ -64,6 +64,9 @@ SYMBOLS = {
     "mcfd_rk_stage_inter": (C.c_int, [_P, C.c_int]),
     "mcfd_rk_stage_time": (C.c_double, [_P, C.c_int]),
     "mcfd_time_step": (C.c_int, [_P, C.c_double, C.c_int, _D]),
+    "mcfd_time_step_device": (C.c_int, [_P, C.c_double, C.c_int, _P]),
+    "mcfd_rk_begin_device": (C.c_int, [_P, C.c_int, C.c_double, _P]),
+    "mcfd_rk_step_device": (C.c_int, [_P, C.c_int, C.c_double, _P]),
     "mcfd_time_step_static": (C.c_int, [C.c_int32, C.c_int32, C.c_int64, _P, _P, C.c_double, C.c_int32, _P, _P]),
     "mcfd_launch_count": (C.c_int64, [_P]),
     "mcfd_enable_kernel_timing": (C.c_int, [_P, C.c_int]),
@@ -249,6 +252,15 @@ class Context:
         dt = C.c_double()
         self._check(self.lib.mcfd_time_step(self.h, dt_guess, rk_order, C.byref(dt)))
         return dt.value
+
+    def time_step_device(self, dt_guess, rk_order, dt_ptr: int):
+        self._check(self.lib.mcfd_time_step_device(self.h, dt_guess, rk_order, _P(dt_ptr)))
+
+    def rk_begin_device(self, order, t, dt_ptr: int):
+        self._check(self.lib.mcfd_rk_begin_device(self.h, order, t, _P(dt_ptr)))
+
+    def rk_step_device(self, order, t, dt_ptr: int):
+        self._check(self.lib.mcfd_rk_step_device(self.h, order, t, _P(dt_ptr)))
 
     def launch_count(self):
         return int(self.lib.mcfd_launch_count(self.h))

@@ -65,6 +65,7 @@ struct StageArgs {
   int block_begin;              // first CTA-sized cell block of this launch
   int mode;
   double dt;
+  const double *dt_dev;         // when not null the time step is read from device memory instead
 };
 
 enum : int {
@@ -443,7 +444,7 @@ MCFD_HD void StagePhaseC(const StageArgs &p, int tid, int bid, double *smem,
   if (!g.active) return;
   const int lc = g.lc;
   double *out = p.u_out + (size_t)g.tile * F * kTile + g.tl;
-  const double dt = p.dt;
+  const double dt = p.dt_dev ? *p.dt_dev : p.dt;
 #pragma unroll
   for (int s = 0; s < G::SLOTS; ++s) {
     const int n = g.Node(s);
@@ -548,6 +549,19 @@ __global__ void TimeStepKernel(const double *u, const double *length, int n_loca
   }
   for (int o = 16; o > 0; o >>= 1) dt = fmin(dt, __shfl_xor_sync(0xffffffffu, dt, o));
   if ((threadIdx.x & 31) == 0) atomicMin(result, (unsigned long long)__double_as_longlong(dt));
+}
+
+// dt = min(cfl * min_dt, dt_guess), doubled and capped again for FR-Lobatto (fem.hpp:433-434,
+// fr/lobatto.hpp:220-222), entirely on the device so that a time loop never has to wait for the host.
+__global__ void TimeStepFinishKernel(const unsigned long long *min_bits, double cfl, double dt_guess,
+    int fr_doubling, double *dt_out) {
+  double dt = fmin(cfl * __longlong_as_double((long long)*min_bits), dt_guess);
+  if (fr_doubling) dt = fmin(dt_guess, 2.0 * dt);
+  *dt_out = dt;
+}
+
+__global__ void TimeStepResetKernel(unsigned long long *min_bits) {
+  *min_bits = (unsigned long long)__double_as_longlong(1e100);
 }
 
 // column[cell*F + f]  <->  tiles[(tile*F + f)*32 + lane]; one CTA per tile, staged through shared

@@ -59,6 +59,8 @@ struct mcfd_ctx {
   // open RK step
   int rk_order = 0, rk_u0 = 0, rk_in = 0;
   double rk_t = 0, rk_dt = 0;
+  const double *rk_dt_dev = nullptr;            // device-resident dt of the open step, or null
+  DevBuf<double> dt_dev;                        // part-local dt computed by mcfd_time_step_device
   mcfd_time_callback time_cb = nullptr;
   void *time_user = nullptr;
   int64_t launches = 0;
@@ -117,7 +119,7 @@ int LaunchStage(mcfd_ctx *ctx, const double *u_in, const double *u0, double *u_o
   a.bkind = ctx->bkind.p; a.bvals = ctx->bvals.p;
   a.n_local = (int)ctx->mesh.n_local;
   a.block_begin = (int)block_begin;
-  a.mode = mode; a.dt = dt;
+  a.mode = mode; a.dt = dt; a.dt_dev = ctx->rk_order ? ctx->rk_dt_dev : nullptr;
   int n_blocks = (int)(block_end - block_begin);
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (ctx->timing) {
@@ -514,6 +516,14 @@ int mcfd_rk_begin(mcfd_ctx *ctx, int order, double t, double dt) {
   ctx->rk_in = ctx->cur;
   ctx->rk_t = t;
   ctx->rk_dt = dt;
+  ctx->rk_dt_dev = nullptr;
+  return MCFD_OK;
+}
+
+int mcfd_rk_begin_device(mcfd_ctx *ctx, int order, double t, const double *dt_dev) {
+  if (!dt_dev) return Fail(ctx, MCFD_ERR_ARG, "null dt_dev");
+  if (int s = mcfd_rk_begin(ctx, order, t, 0.0)) return s;
+  ctx->rk_dt_dev = dt_dev;
   return MCFD_OK;
 }
 
@@ -562,32 +572,43 @@ int mcfd_rk_step(mcfd_ctx *ctx, int order, double t, double dt) {
   return MCFD_OK;
 }
 
-int mcfd_time_step(mcfd_ctx *ctx, double dt_guess, int rk_order, double *dt_local) {
+static const double kCfl[5][9] = {   // fem.hpp:26-37
+  {1.000},
+  {1.000, 0.333},
+  {1.000, 0.333, 0.209, 0.130, 0.089, 0.066, 0.051, 0.040, 0.033},
+  {1.256, 0.409, 0.209, 0.130, 0.089, 0.066, 0.051, 0.040, 0.033},
+  {1.392, 0.464, 0.235, 0.145, 0.100, 0.073, 0.056, 0.045, 0.037}};
+
+int mcfd_time_step_device(mcfd_ctx *ctx, double dt_guess, int rk_order, double *dt_dev) {
   if (int s = RequireMesh(ctx)) return s;
-  if (!dt_local || rk_order < 0 || rk_order > 4) return Fail(ctx, MCFD_ERR_ARG, "bad arguments");
-  // fem.hpp:26-37
-  static const double cfl[5][9] = {
-    {1.000},
-    {1.000, 0.333},
-    {1.000, 0.333, 0.209, 0.130, 0.089, 0.066, 0.051, 0.040, 0.033},
-    {1.256, 0.409, 0.209, 0.130, 0.089, 0.066, 0.051, 0.040, 0.033},
-    {1.392, 0.464, 0.235, 0.145, 0.100, 0.073, 0.056, 0.045, 0.037}};
-  double big = 1e100;
-  unsigned long long bits;
-  std::memcpy(&bits, &big, sizeof(bits));
-  MCFD_CUDA(ctx, cudaMemcpyAsync(ctx->dt_bits.p, &bits, sizeof(bits), cudaMemcpyHostToDevice, ctx->stream));
+  if (rk_order < 0 || rk_order > 4) return Fail(ctx, MCFD_ERR_ARG, "bad RK order");
+  if (!ctx->dt_dev.p) MCFD_CUDA(ctx, ctx->dt_dev.Alloc(1));
+  if (!dt_dev) dt_dev = ctx->dt_dev.p;
+  TimeStepResetKernel<<<1, 1, 0, ctx->stream>>>(ctx->dt_bits.p);
   int n = (int)ctx->mesh.n_local, threads = 128, blocks = (n + threads - 1) / threads;
   if (ctx->q == 3) TimeStepKernel<3><<<blocks, threads, 0, ctx->stream>>>(ctx->u[ctx->cur].p, ctx->length.p, n, ctx->dt_bits.p);
   else TimeStepKernel<4><<<blocks, threads, 0, ctx->stream>>>(ctx->u[ctx->cur].p, ctx->length.p, n, ctx->dt_bits.p);
+  TimeStepFinishKernel<<<1, 1, 0, ctx->stream>>>(ctx->dt_bits.p, kCfl[rk_order][ctx->cfg.degree], dt_guess,
+      ctx->cfg.scheme == MCFD_FR_LOBATTO, dt_dev);
   MCFD_CUDA(ctx, cudaGetLastError());
-  ctx->launches++;
-  MCFD_CUDA(ctx, cudaMemcpyAsync(&bits, ctx->dt_bits.p, sizeof(bits), cudaMemcpyDeviceToHost, ctx->stream));
+  ctx->launches += 3;
+  return MCFD_OK;
+}
+
+int mcfd_time_step(mcfd_ctx *ctx, double dt_guess, int rk_order, double *dt_local) {
+  if (!dt_local) return Fail(ctx, MCFD_ERR_ARG, "bad arguments");
+  if (int s = mcfd_time_step_device(ctx, dt_guess, rk_order, nullptr)) return s;
+  MCFD_CUDA(ctx, cudaMemcpyAsync(dt_local, ctx->dt_dev.p, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
   MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  double min_dt;
-  std::memcpy(&min_dt, &bits, sizeof(bits));
-  double dt = std::min(cfl[rk_order][ctx->cfg.degree] * min_dt, dt_guess);  // fem.hpp:433-434
-  if (ctx->cfg.scheme == MCFD_FR_LOBATTO) dt = std::min(dt_guess, 2.0 * dt);  // fr/lobatto.hpp:220-222
-  *dt_local = dt;
+  return MCFD_OK;
+}
+
+int mcfd_rk_step_device(mcfd_ctx *ctx, int order, double t, const double *dt_dev) {
+  if (int s = mcfd_rk_begin_device(ctx, order, t, dt_dev)) return s;
+  for (int stage = 0; stage < order; ++stage) {
+    if (int s = mcfd_rk_stage_inner(ctx, stage)) { ctx->rk_order = 0; return s; }
+    if (int s = mcfd_rk_stage_inter(ctx, stage)) { ctx->rk_order = 0; return s; }
+  }
   return MCFD_OK;
 }
 
@@ -740,17 +761,13 @@ int mcfd_time_step_static(int32_t scheme, int32_t degree, int64_t n_cells, const
     g_static_dt_address[device] = address;
   }
   double *partials = g_static_dt_address[device];
-  static const double cfl[5][9] = {   // fem.hpp:26-37
-    {1.000}, {1.000, 0.333}, {1.000, 0.333, 0.209, 0.130, 0.089, 0.066, 0.051, 0.040, 0.033},
-    {1.256, 0.409, 0.209, 0.130, 0.089, 0.066, 0.051, 0.040, 0.033},
-    {1.392, 0.464, 0.235, 0.145, 0.100, 0.073, 0.056, 0.045, 0.037}};
   cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
   const int n_blocks = (int)((n_cells + kStaticCellsPerBlock - 1) / kStaticCellsPerBlock);
   if (degree == 2)
     TimeStepPartialsKernel<3><<<n_blocks, kStaticCellsPerBlock * 32, 0, stream>>>(column_dev, length_dev, (int)n_cells, partials);
   else
     TimeStepPartialsKernel<4><<<n_blocks, kStaticCellsPerBlock * 32, 0, stream>>>(column_dev, length_dev, (int)n_cells, partials);
-  TimeStepFinalKernel<<<1, 1024, 0, stream>>>(partials, n_blocks, cfl[rk_order][degree], dt_guess,
+  TimeStepFinalKernel<<<1, 1024, 0, stream>>>(partials, n_blocks, kCfl[rk_order][degree], dt_guess,
       scheme == MCFD_FR_LOBATTO, dt_dev);
   e = cudaGetLastError();
   if (e != cudaSuccess) return Fail(nullptr, MCFD_ERR_CUDA, std::string("mcfd_time_step_static: ") + cudaGetErrorString(e));

@@ -71,6 +71,9 @@ class HaloExchanger:
         self.start()
         self.finish()
 
+    def allreduce_min_tensor(self, t: torch.Tensor):
+        dist.all_reduce(t, op=dist.ReduceOp.MIN, group=self.group)
+
     def allreduce_min(self, value: float) -> float:
         """MPI_Allreduce(MIN) of the time step (demo/euler/sourceless.cpp:194)."""
         dev = self.send.device if self.send is not None else torch.device("cpu")

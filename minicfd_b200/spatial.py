@@ -109,6 +109,13 @@ class Spatial:
         return dt
 
 
+def time_step_device(system: Spatial, dt_guess, rk_order, dt_tensor):
+    """GetTimeStep into a 1-element CUDA tensor, min-reduced over the ranks on the device."""
+    system.ctx.time_step_device(dt_guess, rk_order, dt_tensor.data_ptr())
+    if system.comm is not None:
+        system.comm.allreduce_min_tensor(dt_tensor)
+
+
 class RungeKutta:
     """mini::temporal::RungeKutta<kOrders> (include/mini/temporal/rk.hpp:10-57).  `Update` uses the
     fused stage kernels (mcfd_rk_*); `UpdateGeneric` spells the reference's column algebra out through
@@ -128,6 +135,19 @@ class RungeKutta:
             system.comm.start()            # pack + post sends/recvs (ShareGhostCellCoeffs)
             ctx.rk_stage_inner(stage)      # overlaps the exchange (fem.hpp:249-254)
             system.comm.finish()           # wait + unpack (UpdateGhostCellCoeffs)
+            ctx.rk_stage_inter(stage)
+
+    def UpdateDevice(self, system: Spatial, t, dt_ptr: int):
+        """Update with the time step resident in device memory (no host round trip)."""
+        ctx = system.ctx
+        if system.comm is None:
+            ctx.rk_step_device(self.order, t, dt_ptr)
+            return
+        ctx.rk_begin_device(self.order, t, dt_ptr)
+        for stage in range(self.order):
+            system.comm.start()
+            ctx.rk_stage_inner(stage)
+            system.comm.finish()
             ctx.rk_stage_inter(stage)
 
     def UpdateGeneric(self, system: Spatial, t, dt):
