@@ -131,11 +131,28 @@ class RungeKutta:
             ctx.rk_step(self.order, t, dt)
             return
         ctx.rk_begin(self.order, t, dt)
+        self._stages_with_halo(system)
+
+    def _stages_with_halo(self, system: Spatial):
+        """Every stage: pack + post the exchange, advance the inner cells on the main stream while the
+        messages fly (fem.hpp:249-254), and on a side stream wait for them, unpack and advance the inter
+        cells (fem.hpp:255-256) — the two kernels run concurrently, the streams rejoin before the next stage."""
+        import torch
+        ctx, comm = system.ctx, system.comm
+        main = torch.cuda.current_stream()
+        if getattr(system, "_side_stream", None) is None:
+            system._side_stream = torch.cuda.Stream()
+        side = system._side_stream
         for stage in range(self.order):
-            system.comm.start()            # pack + post sends/recvs (ShareGhostCellCoeffs)
-            ctx.rk_stage_inner(stage)      # overlaps the exchange (fem.hpp:249-254)
-            system.comm.finish()           # wait + unpack (UpdateGhostCellCoeffs)
-            ctx.rk_stage_inter(stage)
+            comm.start()                       # pack on main, sends/receives behind it (ShareGhostCellCoeffs)
+            side.wait_stream(main)             # the stage input is complete
+            ctx.rk_stage_inner(stage)          # main
+            with torch.cuda.stream(side):
+                ctx.set_stream(side.cuda_stream)
+                comm.finish()                  # wait + unpack (UpdateGhostCellCoeffs)
+                ctx.rk_stage_inter(stage)
+                ctx.set_stream(main.cuda_stream)
+            main.wait_stream(side)
 
     def UpdateDevice(self, system: Spatial, t, dt_ptr: int):
         """Update with the time step resident in device memory (no host round trip)."""
@@ -144,11 +161,7 @@ class RungeKutta:
             ctx.rk_step_device(self.order, t, dt_ptr)
             return
         ctx.rk_begin_device(self.order, t, dt_ptr)
-        for stage in range(self.order):
-            system.comm.start()
-            ctx.rk_stage_inner(stage)
-            system.comm.finish()
-            ctx.rk_stage_inter(stage)
+        self._stages_with_halo(system)
 
     def UpdateGeneric(self, system: Spatial, t, dt):
         def euler_next(tt):
