@@ -50,6 +50,7 @@ def parse():
     ap.add_argument("--cpu-cells", type=int, default=0, help="cells per direction of the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of replaying a CUDA graph")
     return ap.parse_args()
 
 
@@ -258,7 +259,41 @@ def ours(args):
     t = 0.0
     for _ in range(max(args.warmup, 3)):
         t += step_device(t)
-    sp.ctx.enable_kernel_timing(True)
+    # One step (GetTimeStep + 3 stages incl. the halo exchange) captured once as a CUDA graph and
+    # replayed: the host launches one graph per step instead of ~10 kernels and 6 NCCL operations.
+    graph = None
+    launches_per_step = None
+    if not args.no_graph and world == 1:   # with NCCL point-to-point inside, replay was slower and did not shut down cleanly
+        try:
+            barrier()
+            l0 = sp.ctx.launch_count()
+            graph = torch.cuda.CUDAGraph()
+            cap_stream = torch.cuda.Stream()
+            cap_stream.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(cap_stream):
+                sp.ctx.set_stream(cap_stream.cuda_stream)
+                with torch.cuda.graph(graph, stream=cap_stream):
+                    step_device(t)
+                sp.ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+            launches_per_step = sp.ctx.launch_count() - l0
+            torch.cuda.current_stream().wait_stream(cap_stream)
+            sp.ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+            for _ in range(3):
+                graph.replay()
+            barrier()
+        except Exception as e:  # capture not possible: fall back to host launches, and say so
+            if rank == 0:
+                print(f"bench.py: CUDA graph capture failed ({type(e).__name__}: {e}); launching from the host",
+                      file=sys.stderr)
+            graph = None
+            sp.ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+
+    def run_step(tt):
+        if graph is not None:
+            graph.replay()
+            return 0.0
+        return step_device(tt)
+
     launches0 = sp.ctx.launch_count()
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -267,14 +302,21 @@ def ours(args):
         clocks.mark_begin()
         e0.record()
         for _ in range(args.steps):
-            t += step_device(t)
+            t += run_step(t)
         e1.record()
         barrier()
         clocks.mark_end()
     ms = e0.elapsed_time(e1)
+    launches = (sp.ctx.launch_count() - launches0) if graph is None else launches_per_step * args.steps
+    # duration of the stage kernel: CUDA events around every stage launch, on the launching stream, over
+    # the same steps launched from the host right after the timed region (events cannot sit in a graph)
+    k_steps = min(args.steps, 20)
+    sp.ctx.enable_kernel_timing(True)
+    for _ in range(k_steps):
+        t += step_device(t)
+    barrier()
     kernel_ms, kernel_launches = sp.ctx.kernel_time(reset=True)
     sp.ctx.enable_kernel_timing(False)
-    launches = sp.ctx.launch_count() - launches0
     tmax = torch.tensor([ms], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
@@ -284,19 +326,18 @@ def ours(args):
     # ---- e2e: host columns in and out every step ---------------------------------------------------
     e2e = None
     if not args.no_e2e:
-        host_in = torch.empty(n_dof_local, dtype=torch.float64, pin_memory=True)
-        host_out = torch.empty(n_dof_local, dtype=torch.float64, pin_memory=True)
-        host_in.numpy()[:] = sp.GetSolutionColumn()
-        e_steps = max(3, min(args.steps, 10))
+        bufs = [torch.empty(n_dof_local, dtype=torch.float64, pin_memory=True) for _ in range(2)]
+        bufs[0].numpy()[:] = sp.GetSolutionColumn()
+        e_steps = max(3, min(args.steps, 20))
 
         def step_e2e(tt):
-            sp.ctx.set_solution(host_in.numpy())          # H2D from pinned memory
-            if comm is not None:
-                pass                                      # ghosts are refreshed inside Update
-            dt = sp.GetTimeStep(1.0, 3)
+            # the user's loop on host columns: SetSolutionColumn(host) -> GetTimeStep -> Update ->
+            # GetSolutionColumn(host); the output buffer of one step is the input of the next
+            sp.ctx.set_solution(bufs[0].numpy())          # H2D from pinned memory (ghosts: refreshed in Update)
+            dt = sp.GetTimeStep(1.0, 3)                   # includes the D2H read of dt
             rk.Update(sp, tt, dt)
-            sp.ctx.get_solution(host_out.numpy())         # D2H of the step's result
-            host_in.copy_(host_out)
+            sp.ctx.get_solution(bufs[1].numpy())          # D2H of the step's result
+            bufs.reverse()
             return dt
         for _ in range(2):
             t += step_e2e(t)
@@ -324,19 +365,21 @@ def ours(args):
         b_alg = 24.0 + 192.0 / sp.kfields
         per_launch_ms = kernel_ms / max(kernel_launches, 1)
         # one launch per stage when there is no ghost layer; with ghosts a stage is two launches
-        launches_per_stage = kernel_launches / (3.0 * args.steps)
+        launches_per_stage = kernel_launches / (3.0 * k_steps)
         achieved = b_alg * n_dof_local / (per_launch_ms * launches_per_stage * 1e-3) / 1e9
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                     "traffic": None, "peak_source": peak_src, "kernel": "mcfd::StageKernel",
                     "algorithmic_bytes_per_dof_update": b_alg, "kernel_ms_per_stage": per_launch_ms * launches_per_stage,
-                    "kernel_share_of_step": kernel_ms / ms}
+                    "kernel_share_of_step": (kernel_ms / k_steps) / (ms / args.steps),
+                    "kernel_timing": f"CUDA events around each stage launch over {k_steps} host-launched steps"}
         traffic_path = os.path.join(ROOT, "profiles", "stage_kernel_traffic.json")
         if os.path.exists(traffic_path):
             roofline["traffic"] = json.load(open(traffic_path)).get("dram_bytes_per_launch")
         line = {"metric": "DOF-updates/s per RK stage (p=2 Euler, hexa)", "value": value, "unit": "DOF-updates/s",
                 "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": config_dict(args, world, dims, f"{px}x{py}x{pz}"), "clocks": clocks.summary(),
+                "config": dict(config_dict(args, world, dims, f"{px}x{py}x{pz}"), cuda_graph=graph is not None),
+                "clocks": clocks.summary(),
                 "roofline": roofline, "gpu_launches": int(launches)}
         if e2e is not None:
             line["e2e"] = e2e
