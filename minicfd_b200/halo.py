@@ -31,10 +31,13 @@ class HaloExchanger:
         self.group = group
         self.send = self.recv = None
         self._reqs = []
+        self._ops = None
+        self.inflight = False     # an exchange of the current state has been posted and not yet unpacked
         self._pack = self._unpack = lambda: None
 
     def bind(self, send: torch.Tensor, recv: torch.Tensor, pack=None, unpack=None):
         self.send, self.recv = send, recv
+        self._ops = None
         if pack is not None:
             self._pack = pack
         if unpack is not None:
@@ -50,15 +53,21 @@ class HaloExchanger:
         ctx.set_stream(torch.cuda.current_stream().cuda_stream)
         self.bind(send, recv, ctx.halo_pack, ctx.halo_unpack)
 
-    def start(self):
-        """ShareGhostCellCoeffs: pack, then post all sends and receives."""
-        self._pack()
+    def _build_ops(self):
         ops = []
         for i, q in enumerate(self.neighbours):
             ops.append(dist.P2POp(dist.irecv, self.recv[self.recv_off[i]:self.recv_off[i + 1]], q, self.group))
         for i, q in enumerate(self.neighbours):
             ops.append(dist.P2POp(dist.isend, self.send[self.send_off[i]:self.send_off[i + 1]], q, self.group))
-        self._reqs = dist.batch_isend_irecv(ops) if ops else []
+        return ops
+
+    def start(self):
+        """ShareGhostCellCoeffs: pack, then post all sends and receives (one NCCL group)."""
+        self._pack()
+        if self._ops is None:
+            self._ops = self._build_ops()      # the buffers never move: build the descriptors once
+        self._reqs = dist.batch_isend_irecv(self._ops) if self._ops else []
+        self.inflight = True
 
     def finish(self):
         """UpdateGhostCellCoeffs: wait for the messages, then unpack into the ghost cells."""
@@ -66,10 +75,17 @@ class HaloExchanger:
             r.wait()
         self._reqs = []
         self._unpack()
+        self.inflight = False
 
     def exchange(self):
-        self.start()
+        """Make the ghost cells of the current state current (reuses an exchange already in flight)."""
+        if not self.inflight:
+            self.start()
         self.finish()
+
+    def drain(self):
+        if self.inflight:
+            self.finish()
 
     def allreduce_min_tensor(self, t: torch.Tensor):
         dist.all_reduce(t, op=dist.ReduceOp.MIN, group=self.group)

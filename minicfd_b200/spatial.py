@@ -90,6 +90,8 @@ class Spatial:
         self._t = t
 
     def SetSolutionColumn(self, column):
+        if self.comm is not None:
+            self.comm.drain()              # an exchange of the old state may still be in flight
         self.ctx.set_solution(column)
 
     def GetSolutionColumn(self):
@@ -134,25 +136,32 @@ class RungeKutta:
         self._stages_with_halo(system)
 
     def _stages_with_halo(self, system: Spatial):
-        """Every stage: pack + post the exchange, advance the inner cells on the main stream while the
-        messages fly (fem.hpp:249-254), and on a side stream wait for them, unpack and advance the inter
-        cells (fem.hpp:255-256) — the two kernels run concurrently, the streams rejoin before the next stage."""
+        """Every stage: the inner cells advance on the main stream (fem.hpp:249-254) while a high-priority
+        side stream waits for the ghost data, unpacks it, advances the inter cells (fem.hpp:255-256) and at
+        once packs and posts the exchange of the *next* stage input — the send cells are inter cells, so
+        their new values exist as soon as the small inter kernel is done, long before the inner kernel is."""
         import torch
         ctx, comm = system.ctx, system.comm
         main = torch.cuda.current_stream()
         if getattr(system, "_side_stream", None) is None:
-            system._side_stream = torch.cuda.Stream()
+            system._side_stream = torch.cuda.Stream(priority=-1)
         side = system._side_stream
+        if not comm.inflight:                  # first stage after a SetSolutionColumn: post the exchange now
+            comm.start()
         for stage in range(self.order):
-            comm.start()                       # pack on main, sends/receives behind it (ShareGhostCellCoeffs)
-            side.wait_stream(main)             # the stage input is complete
+            inner_input_ready = torch.cuda.Event()
+            inner_input_ready.record(main)     # everything queued on main so far (incl. the previous inner kernel)
             ctx.rk_stage_inner(stage)          # main
             with torch.cuda.stream(side):
                 ctx.set_stream(side.cuda_stream)
+                side.wait_event(inner_input_ready)
                 comm.finish()                  # wait + unpack (UpdateGhostCellCoeffs)
                 ctx.rk_stage_inter(stage)
+                inter_done = torch.cuda.Event()
+                inter_done.record(side)
+                comm.start()                   # pack the new inter-cell values, post the next exchange
                 ctx.set_stream(main.cuda_stream)
-            main.wait_stream(side)
+            main.wait_event(inter_done)
 
     def UpdateDevice(self, system: Spatial, t, dt_ptr: int):
         """Update with the time step resident in device memory (no host round trip)."""

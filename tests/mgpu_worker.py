@@ -23,7 +23,7 @@ def main():
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
     torch.cuda.set_device(local)
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    os.environ.setdefault("TORCH_NCCL_HIGH_PRIORITY", "1"); dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     degree = int(sys.argv[1]) if len(sys.argv) > 1 else 2
     px, py, pz = meshmod.factor3(world)
     m = meshmod.box(4 * px, 4 * py, 3 * pz, warp=0.1, seed=3)
@@ -68,6 +68,7 @@ def main():
         ok = e_u < 1e-12 and e_r < 1e-11
     flag = torch.tensor([1.0 if ok else 0.0], device="cuda")
     dist.broadcast(flag, 0)
+    comm.drain(); torch.cuda.synchronize()
     dist.destroy_process_group()
     if flag.item() != 1.0:
         sys.exit(1)
