@@ -526,29 +526,40 @@ void RunStageBlockOnHost(const StageArgs &p, int bid, double *smem) {
 #endif
 
 #ifdef __CUDACC__
-// FiniteElement::GetTimeStep's reduction (fem.hpp:417-432; rotated/euler.hpp:340-345): one thread per
-// cell, min over cells of length / max(1e-5, max_nodes(c + |v|)), folded into *result by atomicMin
-// on the bit pattern (valid for non-negative doubles).
+// FiniteElement::GetTimeStep's reduction (fem.hpp:417-432; rotated/euler.hpp:340-345): min over cells of
+// length / max(1e-5, max_nodes(c + |v|)).  One CTA per tile, lanes = cells, the nodes dealt to the warps
+// (whole 256-byte rows per load); per-cell maxima meet in shared memory, the CTA's minimum is folded
+// into *result by atomicMin on the bit pattern (valid for non-negative doubles).
 template <int Q>
-__global__ void TimeStepKernel(const double *u, const double *length, int n_local,
+__global__ void __launch_bounds__(256) TimeStepKernel(const double *u, const double *length, int n_local,
     unsigned long long *result) {
-  constexpr int N = Q * Q * Q, F = 5 * N;
-  int cell = blockIdx.x * blockDim.x + threadIdx.x;
-  double dt = 1e100;
+  constexpr int N = Q * Q * Q, F = 5 * N, NW = 8;
+  __shared__ double s_max[NW][kTile];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cell = blockIdx.x * kTile + lane;
+  const double *src = u + (size_t)blockIdx.x * F * kTile + lane;
+  double vmax = 1e-5;
   if (cell < n_local) {
-    const double *src = u + (size_t)(cell >> 5) * F * kTile + (cell & 31);
-    double vmax = 1e-5;
-    for (int n = 0; n < N; ++n) {
+    for (int n = warp; n < N; n += NW) {
       Prim q = ConsToPrim(src[(n * 5) * kTile], src[(n * 5 + 1) * kTile], src[(n * 5 + 2) * kTile],
                           src[(n * 5 + 3) * kTile], src[(n * 5 + 4) * kTile]);
       double c = SoundSpeed(q.rho, q.p);
       double v = sqrt(q.u * q.u + q.v * q.v + q.w * q.w);
       vmax = fmax(vmax, fmax(c + v, c - v));
     }
-    dt = length[cell] / vmax;
   }
-  for (int o = 16; o > 0; o >>= 1) dt = fmin(dt, __shfl_xor_sync(0xffffffffu, dt, o));
-  if ((threadIdx.x & 31) == 0) atomicMin(result, (unsigned long long)__double_as_longlong(dt));
+  s_max[warp][lane] = vmax;
+  __syncthreads();
+  if (warp == 0) {
+    double dt = 1e100;
+    if (cell < n_local) {
+#pragma unroll
+      for (int w = 1; w < NW; ++w) vmax = fmax(vmax, s_max[w][lane]);
+      dt = length[cell] / vmax;
+    }
+    for (int o = 16; o > 0; o >>= 1) dt = fmin(dt, __shfl_xor_sync(0xffffffffu, dt, o));
+    if (lane == 0) atomicMin(result, (unsigned long long)__double_as_longlong(dt));
+  }
 }
 
 // dt = min(cfl * min_dt, dt_guess), doubled and capped again for FR-Lobatto (fem.hpp:433-434,

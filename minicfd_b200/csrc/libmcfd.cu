@@ -585,7 +585,7 @@ int mcfd_time_step_device(mcfd_ctx *ctx, double dt_guess, int rk_order, double *
   if (!ctx->dt_dev.p) MCFD_CUDA(ctx, ctx->dt_dev.Alloc(1));
   if (!dt_dev) dt_dev = ctx->dt_dev.p;
   TimeStepResetKernel<<<1, 1, 0, ctx->stream>>>(ctx->dt_bits.p);
-  int n = (int)ctx->mesh.n_local, threads = 128, blocks = (n + threads - 1) / threads;
+  int n = (int)ctx->mesh.n_local, threads = 256, blocks = (n + kTile - 1) / kTile;
   if (ctx->q == 3) TimeStepKernel<3><<<blocks, threads, 0, ctx->stream>>>(ctx->u[ctx->cur].p, ctx->length.p, n, ctx->dt_bits.p);
   else TimeStepKernel<4><<<blocks, threads, 0, ctx->stream>>>(ctx->u[ctx->cur].p, ctx->length.p, n, ctx->dt_bits.p);
   TimeStepFinishKernel<<<1, 1, 0, ctx->stream>>>(ctx->dt_bits.p, kCfl[rk_order][ctx->cfg.degree], dt_guess,
