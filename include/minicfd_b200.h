@@ -195,6 +195,12 @@ int mcfd_time_step_static(int32_t scheme, int32_t degree, int64_t n_cells, const
                           const double *length_dev, double dt_guess, int32_t rk_order, double *dt_dev,
                           void *cuda_stream);
 
+/* Initial-condition clean-up on the current solution of the local cells: kind 0 =
+ * mini::limiter::average::Reconstruct (include/mini/limiter/average.hpp:11-28), kind 1 =
+ * mini::limiter::majority::Reconstruct (include/mini/limiter/majority.hpp:14-42), as called by
+ * demo/euler/sourceless.cpp:146-153.  Ghost cells are not touched: exchange afterwards. */
+int mcfd_limiter_reconstruct(mcfd_ctx *ctx, int kind);
+
 /* -- diagnostics --------------------------------------------------------------------------------- */
 
 /* Number of kernels this context has launched so far (bench.py's gpu_launches). */

@@ -68,6 +68,7 @@ SYMBOLS = {
     "mcfd_rk_begin_device": (C.c_int, [_P, C.c_int, C.c_double, _P]),
     "mcfd_rk_step_device": (C.c_int, [_P, C.c_int, C.c_double, _P]),
     "mcfd_time_step_static": (C.c_int, [C.c_int32, C.c_int32, C.c_int64, _P, _P, C.c_double, C.c_int32, _P, _P]),
+    "mcfd_limiter_reconstruct": (C.c_int, [_P, C.c_int]),
     "mcfd_launch_count": (C.c_int64, [_P]),
     "mcfd_enable_kernel_timing": (C.c_int, [_P, C.c_int]),
     "mcfd_kernel_time": (C.c_int, [_P, _D, _I64, C.c_int]),
@@ -261,6 +262,9 @@ class Context:
 
     def rk_step_device(self, order, t, dt_ptr: int):
         self._check(self.lib.mcfd_rk_step_device(self.h, order, t, _P(dt_ptr)))
+
+    def limiter_reconstruct(self, kind):
+        self._check(self.lib.mcfd_limiter_reconstruct(self.h, kind))
 
     def launch_count(self):
         return int(self.lib.mcfd_launch_count(self.h))

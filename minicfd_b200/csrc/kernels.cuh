@@ -40,6 +40,7 @@ constexpr int kP2Cells = MCFD_P2_CELLS, kP2Warps = MCFD_P2_WARPS, kP3Cells = 16,
 // Per-degree tables, filled by the host (tables.cpp) and copied to constant memory.
 struct Tables {
   double xi[kMaxQ];                    // Lobatto points (integrator/lobatto.hpp:38-57)
+  double w[kMaxQ];                     // Lobatto weights
   double a[kMaxQ][kMaxQ];              // R[c] += a[i][m] * Fhat_d(node m on the d-line)[c]
   double coef_f;                       // R -= coef_f * |n| * f_upwind
   double coef_F;                       // R += coef_F * sgn * Fhat_d   (0 for DG)
@@ -560,6 +561,43 @@ __global__ void __launch_bounds__(256) TimeStepKernel(const double *u, const dou
     for (int o = 16; o > 0; o >>= 1) dt = fmin(dt, __shfl_xor_sync(0xffffffffu, dt, o));
     if (lane == 0) atomicMin(result, (unsigned long long)__double_as_longlong(dt));
   }
+}
+
+// Initial-condition clean-up limiters (limiter/average.hpp:11-28, limiter/majority.hpp:14-42): every node
+// of a cell gets the cell average (sum_q u_q w_q detJ_q / volume, polynomial/hexahedron.hpp:626-632) or,
+// per component, the value that more than half of the nodes carry.  One thread per cell.
+template <int Q>
+__global__ void CellConstantKernel(double *u, const double *geom, int n_local, int majority) {
+  constexpr int N = Q * Q * Q, F = 5 * N;
+  const int cell = blockIdx.x * blockDim.x + threadIdx.x;
+  if (cell >= n_local) return;
+  double *dst = u + (size_t)(cell >> 5) * F * kTile + (cell & 31);
+  double value[5] = {0, 0, 0, 0, 0};
+  if (majority) {
+    for (int k = 0; k < 5; ++k) {
+      bool found = false;
+      for (int q = 0; q < N && !found; ++q) {
+        const double val = dst[(q * 5 + k) * kTile];
+        int count = 0;
+        for (int r = 0; r < N; ++r) count += dst[(r * 5 + k) * kTile] == val;
+        if (count * 2 > N) { value[k] = val; found = true; }
+      }
+      // the reference asserts that a majority exists; without one it leaves value[k] unset
+    }
+  } else {
+    const double *g = geom + (size_t)(cell >> 5) * kGeomRows * kTile + (cell & 31);
+    double volume = 0;
+    for (int q = 0; q < N; ++q) {
+      const int i = q / (Q * Q), j = (q / Q) % Q, k = q % Q;
+      const Metric m = ComputeMetric(g, kTile, c_tab.xi[i], c_tab.xi[j], c_tab.xi[k]);
+      const double w = c_tab.w[i] * c_tab.w[j] * c_tab.w[k] * m.det;   // global weight
+      volume += w;
+      for (int c = 0; c < 5; ++c) value[c] += dst[(q * 5 + c) * kTile] * w;
+    }
+    for (int c = 0; c < 5; ++c) value[c] /= volume;
+  }
+  for (int q = 0; q < N; ++q)
+    for (int c = 0; c < 5; ++c) dst[(q * 5 + c) * kTile] = value[c];
 }
 
 // dt = min(cfl * min_dt, dt_guess), doubled and capped again for FR-Lobatto (fem.hpp:433-434,

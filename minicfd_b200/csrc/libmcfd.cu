@@ -612,6 +612,18 @@ int mcfd_rk_step_device(mcfd_ctx *ctx, int order, double t, const double *dt_dev
   return MCFD_OK;
 }
 
+int mcfd_limiter_reconstruct(mcfd_ctx *ctx, int kind) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (kind != 0 && kind != 1) return Fail(ctx, MCFD_ERR_ARG, "limiter kind must be 0 (average) or 1 (majority)");
+  if (ctx->rk_order) return Fail(ctx, MCFD_ERR_STATE, "an RK step is open");
+  int n = (int)ctx->mesh.n_local, threads = 128, blocks = (n + threads - 1) / threads;
+  if (ctx->q == 3) CellConstantKernel<3><<<blocks, threads, 0, ctx->stream>>>(ctx->u[ctx->cur].p, ctx->geom.p, n, kind);
+  else CellConstantKernel<4><<<blocks, threads, 0, ctx->stream>>>(ctx->u[ctx->cur].p, ctx->geom.p, n, kind);
+  MCFD_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  return MCFD_OK;
+}
+
 int64_t mcfd_launch_count(const mcfd_ctx *ctx) { return ctx ? ctx->launches : 0; }
 
 int mcfd_enable_kernel_timing(mcfd_ctx *ctx, int enable) {

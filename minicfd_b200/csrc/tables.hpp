@@ -95,7 +95,7 @@ inline Tables BuildTables(int degree, int scheme, int n_warps, int sub) {
   const int q = degree + 1, n = q * q * q, fq = q * q;
   double x[kMaxQ], w[kMaxQ];
   LobattoRule(q, x, w);
-  for (int i = 0; i < q; ++i) t.xi[i] = x[i];
+  for (int i = 0; i < q; ++i) { t.xi[i] = x[i]; t.w[i] = w[i]; }
   const double g_prime = HuynhLumpedGPrimeAtOne(degree);
   for (int i = 0; i < q; ++i) {
     for (int m = 0; m < q; ++m) {

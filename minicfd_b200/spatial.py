@@ -118,6 +118,16 @@ def time_step_device(system: Spatial, dt_guess, rk_order, dt_tensor):
         system.comm.allreduce_min_tensor(dt_tensor)
 
 
+def average_reconstruct(system: Spatial):
+    """mini::limiter::average::Reconstruct(part) (limiter/average.hpp:11-28)."""
+    system.ctx.limiter_reconstruct(0)
+
+
+def majority_reconstruct(system: Spatial):
+    """mini::limiter::majority::Reconstruct(part) (limiter/majority.hpp:14-42)."""
+    system.ctx.limiter_reconstruct(1)
+
+
 class RungeKutta:
     """mini::temporal::RungeKutta<kOrders> (include/mini/temporal/rk.hpp:10-57).  `Update` uses the
     fused stage kernels (mcfd_rk_*); `UpdateGeneric` spells the reference's column algebra out through

@@ -711,6 +711,32 @@ double oracle_time_step(void *h, const double *u, double dt_guess, int rk_order)
   return dt;
 }
 
+/* limiter/average.hpp:11-28 (kind 0) and limiter/majority.hpp:14-42 (kind 1) on a column */
+void oracle_limiter(void *h, int kind, double *u) {
+  oracle_t *o = h;
+  int q = o->q, n = o->n, fq = q * q;
+  for (int64_t c = 0; c < o->n_cells; ++c) {
+    double value[5] = {0, 0, 0, 0, 0};
+    if (kind == 0) { /* polynomial/hexahedron.hpp:626-632 */
+      double volume = 0;
+      for (int a = 0; a < n; ++a) {
+        double w = o->w[a / fq] * o->w[(a / q) % q] * o->w[a % q] * o->det[c * n + a];
+        volume += w;
+        for (int k = 0; k < 5; ++k) value[k] += u[(c * n + a) * 5 + k] * w;
+      }
+      for (int k = 0; k < 5; ++k) value[k] /= volume;
+    } else {
+      for (int k = 0; k < 5; ++k)
+        for (int a = 0; a < n; ++a) {
+          int cnt = 0;
+          for (int b = 0; b < n; ++b) cnt += u[(c * n + b) * 5 + k] == u[(c * n + a) * 5 + k];
+          if (cnt * 2 > n) { value[k] = u[(c * n + a) * 5 + k]; break; }
+        }
+    }
+    for (int a = 0; a < n; ++a) for (int k = 0; k < 5; ++k) u[(c * n + a) * 5 + k] = value[k];
+  }
+}
+
 /* one rotated Riemann problem (test hook) */
 void oracle_riemann_flux(int riemann, int bc_kind, const double *frame9, const double *ul, const double *ur,
     double *f) {

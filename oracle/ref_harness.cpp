@@ -45,6 +45,11 @@
 #include "mini/integrator/hexahedron.hpp"
 #include "mini/integrator/lobatto.hpp"
 #include "mini/integrator/quadrangle.hpp"
+#include "mini/limiter/average.hpp"
+// limiter/majority.hpp:27 names `Scalar` unqualified; the drivers define that alias at global scope before
+// including it (demo/euler/sourceless.hpp:11), and so do we.
+using Scalar = double;
+#include "mini/limiter/majority.hpp"
 #include "mini/polynomial/hexahedron.hpp"
 #include "mini/riemann/euler/ausm.hpp"
 #include "mini/riemann/euler/exact.hpp"
@@ -535,6 +540,7 @@ struct SolverBase {
   virtual void rk_update(int order, double t, double dt, int n_steps) = 0;
   virtual double time_step(double dt_guess, int rk_order) const = 0;
   virtual void cell_geometry(int r, double *length, double *volume) const = 0;
+  virtual void limiter(int kind) = 0;
 };
 
 template <class Spatial>
@@ -652,6 +658,12 @@ struct SolverImpl : SolverBase {
     double dt = dt_guess;  // MPI_Allreduce(MIN), sourceless.cpp:191-194
     for (auto &sp : spatials) dt = std::min(dt, sp->GetTimeStep(dt_guess, rk_order));
     return dt;
+  }
+  void limiter(int kind) override {
+    for (auto &p : parts) {
+      if (kind == 0) mini::limiter::average::Reconstruct(p.get());
+      else mini::limiter::majority::Reconstruct(p.get());
+    }
   }
   void cell_geometry(int r, double *length, double *volume) const override {
     for (auto &c : parts[r]->local_cells_) {
@@ -772,6 +784,7 @@ void REF_FN(rk_update)(void *h, int order, double t, double dt, int n_steps) {
 double REF_FN(time_step)(void *h, double dt_guess, int rk_order) {
   return static_cast<SolverBase *>(h)->time_step(dt_guess, rk_order);
 }
+void REF_FN(limiter)(void *h, int kind) { static_cast<SolverBase *>(h)->limiter(kind); }
 void REF_FN(cell_geometry)(void *h, int r, double *length, double *volume) {
   static_cast<SolverBase *>(h)->cell_geometry(r, length, volume);
 }

@@ -78,6 +78,11 @@ class Oracle:
         lib().oracle_rk_update(self.h, C.c_int(order), C.c_double(t), C.c_double(dt), _dp(u))
         return u
 
+    def limiter(self, u, kind):
+        u = np.array(u, dtype=np.float64, copy=True)
+        lib().oracle_limiter(self.h, C.c_int(kind), _dp(u))
+        return u
+
     def time_step(self, u, dt_guess, rk_order):
         u = np.ascontiguousarray(u, dtype=np.float64)
         return float(lib().oracle_time_step(self.h, _dp(u), C.c_double(dt_guess), C.c_int(rk_order)))

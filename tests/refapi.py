@@ -147,6 +147,9 @@ class Ref:
         f = self._f("time_step"); f.restype = C.c_double
         return float(f(self.h, C.c_double(dt_guess), C.c_int(rk_order)))
 
+    def limiter(self, kind):
+        self._f("limiter")(self.h, C.c_int(kind))
+
     def cell_geometry(self, r=0):
         n = self.count_local(r)
         length = np.empty(n); volume = np.empty(n)

@@ -298,3 +298,29 @@ def test_device_resident_time_step_and_update():
         assert float(dt_dev.item()) == dt
     got = b.GetSolutionColumn()
     assert np.isfinite(got).all() and np.array_equal(a.GetSolutionColumn(), got)
+
+
+@pytest.mark.parametrize("degree", [2, 3])
+@pytest.mark.parametrize("kind", [0, 1])
+def test_initial_limiters(degree, kind):
+    """average::Reconstruct / majority::Reconstruct on the device vs the oracle."""
+    from minicfd_b200.spatial import average_reconstruct, majority_reconstruct
+    m = cases.small_mesh(seed=5)
+    n = (degree + 1) ** 3
+    rng = np.random.default_rng(1)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), seed=3).reshape(m.n_cells, n, 5)
+    if kind == 1:
+        maj = u[:, :1, :].copy()
+        mask = rng.random((m.n_cells, n, 1)) < 0.7
+        mask[:, : n // 2 + 2] = True
+        u = np.where(mask, maj, u)
+    u = u.reshape(-1)
+    sp = make_spatial(m, degree, 0, capi.HLLC)
+    sp.SetSolutionColumn(u)
+    (average_reconstruct if kind == 0 else majority_reconstruct)(sp)
+    expect = oc.Oracle(m, degree).limiter(u, kind)
+    got = sp.GetSolutionColumn()
+    if kind == 1:
+        assert np.array_equal(got, expect)          # pure selection: bit-exact
+    else:
+        assert relerr(got, expect) < TOL

@@ -132,3 +132,26 @@ def test_rotated_riemann_matches_reference(kind):
         assert np.abs(a - b).max() <= 1e-12 * max(1.0, np.abs(a).max())
         w = oc.riemann_flux(kind, frame, ul, ur, bc=0)
         assert np.abs(w - r.riemann_flux(kind, frame, ul, ur, bc=0)).max() < 1e-14
+
+
+@pytest.mark.skipif(not refapi.available(2), reason="oracle/_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("degree", [2, 3])
+@pytest.mark.parametrize("kind", [0, 1])
+def test_initial_limiters_match_reference(degree, kind):
+    """limiter/average.hpp and limiter/majority.hpp (demo/euler/sourceless.cpp:146-153)."""
+    m = cases.small_mesh(seed=5)
+    n = (degree + 1) ** 3
+    rng = np.random.default_rng(1)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), seed=3).reshape(m.n_cells, n, 5)
+    if kind == 1:   # give every cell a strict majority value per component
+        maj = u[:, :1, :].copy()
+        mask = rng.random((m.n_cells, n, 1)) < 0.7
+        mask[:, : n // 2 + 2] = True
+        u = np.where(mask, maj, u)
+    u = u.reshape(-1)
+    r = refapi.Ref(m, degree=degree)
+    r.set_solution(u)
+    r.limiter(kind)
+    o = oc.Oracle(m, degree)
+    got, ref = o.limiter(u, kind), r.get_solution()
+    assert np.abs(got - ref).max() <= 1e-14 * np.abs(ref).max()
