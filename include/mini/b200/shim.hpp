@@ -328,8 +328,8 @@ class FiniteElementB200 : public temporal::System<typename P::Scalar> {
   using Column = typename temporal::System<Scalar>::Column;
   using Function = std::function<Value(const Global &, double)>;  // fem.hpp:72
 
-  explicit FiniteElementB200(Part *part_ptr, int device = -1) : part_ptr_(part_ptr) {
-    mcfd_config cfg{kScheme, Part::kDegrees, Riemann::kKind, device};
+  explicit FiniteElementB200(Part *part_ptr, int device = -1, double c_next = 0.0) : part_ptr_(part_ptr) {
+    mcfd_config cfg{kScheme, Part::kDegrees, Riemann::kKind, device, c_next};
     if (mcfd_create(&cfg, &ctx_) != 0) throw std::runtime_error(std::string("mcfd_create: ") + mcfd_last_error(nullptr));
     auto &p = *part_ptr_;
     b200::Check(mcfd_set_mesh(ctx_, (int64_t)p.nodes_.size() / 3, p.nodes_.data(), p.n_local_, p.n_ghost_,
@@ -443,6 +443,12 @@ class Lobatto : public FiniteElementB200<P, R, MCFD_FR_LOBATTO> {  // spatial/fr
  public:
   using FiniteElementB200<P, R, MCFD_FR_LOBATTO>::FiniteElementB200;
   std::string name() const { return "FR::Lobatto"; }
+};
+template <typename P, typename R>
+class General : public FiniteElementB200<P, R, MCFD_FR_GENERAL> {  // spatial/fr/general.hpp:34-641
+ public:
+  General(P *part_ptr, typename P::Scalar c_next) : FiniteElementB200<P, R, MCFD_FR_GENERAL>(part_ptr, -1, c_next) {}
+  std::string name() const { return "FR::General"; }
 };
 }  // namespace fr
 namespace dg {

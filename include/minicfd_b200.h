@@ -42,7 +42,9 @@ typedef enum {
 
 /* Spatial scheme: include/mini/spatial/fr/lobatto.hpp:36-434 (Huynh-lumped FR on Lobatto points)
  * or include/mini/spatial/dg/lobatto.hpp:32-303 (DGSEM). */
-typedef enum { MCFD_FR_LOBATTO = 0, MCFD_DG_LOBATTO = 1 } mcfd_scheme;
+/* MCFD_FR_GENERAL: include/mini/spatial/fr/general.hpp:34-641, the Vincent correction function with the
+ * given c_next spread over the whole node line (basis/vincent.hpp:18-102). */
+typedef enum { MCFD_FR_LOBATTO = 0, MCFD_DG_LOBATTO = 1, MCFD_FR_GENERAL = 2 } mcfd_scheme;
 
 /* Riemann solver behind mini::riemann::rotated::Euler<...> (include/mini/riemann/rotated/euler.hpp:
  * 153-159): include/mini/riemann/euler/exact.hpp:44-46, hllc.hpp:30-44, ausm.hpp:30-33. */
@@ -66,6 +68,7 @@ typedef struct {
   int32_t degree;    /* P: 2 or 3 (template parameter kDegrees, demo/euler/sourceless.hpp:27) */
   int32_t riemann;   /* mcfd_riemann */
   int32_t device;    /* CUDA device ordinal, -1 = current device */
+  double fr_c_next;  /* MCFD_FR_GENERAL only: the `c_next` of fr::General(part, c_next), fr/general.hpp:218-219 */
 } mcfd_config;
 
 /* -- life cycle ------------------------------------------------------------------------------ */

@@ -10,7 +10,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libminicfd_b200.so")
 
-FR_LOBATTO, DG_LOBATTO = 0, 1
+FR_LOBATTO, DG_LOBATTO, FR_GENERAL = 0, 1, 2
 EXACT, HLLC, AUSM = 0, 1, 2
 (BC_INVISCID_WALL, BC_SUPERSONIC_OUTLET, BC_SUPERSONIC_INLET, BC_SUBSONIC_INLET, BC_SUBSONIC_OUTLET,
  BC_SMART, BC_NO_SLIP_WALL) = range(7)
@@ -19,7 +19,8 @@ TIME_CALLBACK = C.CFUNCTYPE(None, C.c_void_p, C.c_double)
 
 
 class Config(C.Structure):
-    _fields_ = [("scheme", C.c_int32), ("degree", C.c_int32), ("riemann", C.c_int32), ("device", C.c_int32)]
+    _fields_ = [("scheme", C.c_int32), ("degree", C.c_int32), ("riemann", C.c_int32), ("device", C.c_int32),
+                ("fr_c_next", C.c_double)]
 
 
 class McfdError(RuntimeError):
@@ -117,10 +118,10 @@ def time_step_static(scheme, degree, n_cells, column_ptr, length_ptr, dt_guess, 
 class Context:
     """One mcfd_ctx: a part of the mesh resident on one GPU."""
 
-    def __init__(self, scheme=FR_LOBATTO, degree=2, riemann=HLLC, device=-1):
+    def __init__(self, scheme=FR_LOBATTO, degree=2, riemann=HLLC, device=-1, fr_c_next=0.0):
         self.lib = load()
         self.h = _P()
-        cfg = Config(scheme, degree, riemann, device)
+        cfg = Config(scheme, degree, riemann, device, fr_c_next)
         rc = self.lib.mcfd_create(C.byref(cfg), C.byref(self.h))
         if rc != 0:
             raise McfdError(f"mcfd_create failed ({rc}): {self.lib.mcfd_last_error(None).decode()}")

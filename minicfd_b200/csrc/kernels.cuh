@@ -44,6 +44,10 @@ struct Tables {
   double a[kMaxQ][kMaxQ];              // R[c] += a[i][m] * Fhat_d(node m on the d-line)[c]
   double coef_f;                       // R -= coef_f * |n| * f_upwind
   double coef_F;                       // R += coef_F * sgn * Fhat_d   (0 for DG)
+  // general Vincent correction (fr/general.hpp:85-211): g'(xi_i) of the correction function of the
+  // - and + end of a node line; the lumped Lobatto scheme only has g[0][0] and g[1][Q-1]
+  int general;
+  double g[2][kMaxQ];
   int slot_node[kMaxWarps * kMaxSlots];  // node handled by (warp, slot), -1 = idle
   // face-point index q of node n on its face in direction d (or -1 when not on a face)
   signed char node_q[kMaxN][3];
@@ -279,7 +283,7 @@ MCFD_HD void StagePhaseA(const StageArgs &p, int tid, int bid, double *smem,
 
 // ---- phase B1: flux divergence along the three node lines + the node's own face-flux terms ------
 // (fr/general.hpp:280-286, 290-294, 305-313; dg/lobatto.hpp:161-170)
-template <int Q, int CPB, int NW>
+template <int Q, int CPB, int NW, bool kGeneral>
 MCFD_HD void StagePhaseB1(const StageArgs &p, int tid, int bid, double *smem, SlotResiduals<Q, CPB, NW> *res) {
   using G = StageGeometry<Q, CPB, NW>;
   G g(p, tid, bid, smem);
@@ -303,7 +307,15 @@ MCFD_HD void StagePhaseB1(const StageArgs &p, int tid, int bid, double *smem, Sl
 #pragma unroll
           for (int c = 0; c < 5; ++c) r[c] = fma(a, src[c * CPB], r[c]);
         }
-        if (id == 0 || id == Q - 1) {               // the node lies on a face in direction d
+        if (kGeneral) {                             // both line ends correct every node of the line
+#pragma unroll
+          for (int side = 0; side < 2; ++side) {
+            const double gg = c_tab.g[side][id];
+            const double *end = g.sF + ((size_t)(base + (side ? (Q - 1) * st : 0)) * 15 + d * 5) * CPB + lc;
+#pragma unroll
+            for (int c = 0; c < 5; ++c) r[c] = fma(gg, end[c * CPB], r[c]);
+          }
+        } else if (id == 0 || id == Q - 1) {        // the node lies on a face in direction d
           const double cF = id != 0 ? c_tab.coef_F : -c_tab.coef_F;
           const double *own = g.sF + ((size_t)n * 15 + d * 5) * CPB + lc;
 #pragma unroll
@@ -358,7 +370,7 @@ MCFD_HD void LoadPoint(const StageArgs &p, const StageGeometry<Q, CPB, NW> &g, i
   }
 }
 
-template <int Q, int kRiemann, int CPB, int NW>
+template <int Q, int kRiemann, int CPB, int NW, bool kGeneral>
 MCFD_HD void StagePhaseB2(const StageArgs &p, int tid, int bid, double *smem) {
   using G = StageGeometry<Q, CPB, NW>;
   G g(p, tid, bid, smem);
@@ -382,7 +394,8 @@ MCFD_HD void StagePhaseB2(const StageArgs &p, int tid, int bid, double *smem) {
       const double n2 = nx * nx + ny * ny + nz * nz;
       const double inv_area = Rsqrt(n2), area = n2 * inv_area;
       double fl[5];
-      double scale = -c_tab.coef_f * area;           // lifting coefficient; 1/det is applied in phase C
+      // lumped: the lifted term itself; general: |n| f* along my outward normal, lifted in phase C
+      double scale = kGeneral ? area : -c_tab.coef_f * area;
       if (cur.nb >= 0) {
         // The Riemann problem is posed in the holder's frame, as the reference does: when the
         // neighbour holds the face, swap the states, flip the normal and negate the result.
@@ -416,7 +429,7 @@ MCFD_HD void StagePhaseB2(const StageArgs &p, int tid, int bid, double *smem) {
           }
 #pragma unroll
           for (int c = 0; c < 5; ++c) fl[c] = fm[c][0] * nx + fm[c][1] * ny + fm[c][2] * nz;
-          scale = -c_tab.coef_F * sgn;
+          scale = kGeneral ? sgn : -c_tab.coef_F * sgn;
         } else {
           State5 ui, given;
           const double *gv = p.bvals + ((size_t)b * FQ + q) * 5;
@@ -436,7 +449,7 @@ MCFD_HD void StagePhaseB2(const StageArgs &p, int tid, int bid, double *smem) {
 }
 
 // ---- phase C: gather the face terms, RK update, store ---------------------------------------------
-template <int Q, int CPB, int NW>
+template <int Q, int CPB, int NW, bool kGeneral>
 MCFD_HD void StagePhaseC(const StageArgs &p, int tid, int bid, double *smem,
     const SlotStates<Q, CPB, NW> &su, const SlotStates<Q, CPB, NW> &su0, const SlotResiduals<Q, CPB, NW> &sres) {
   using G = StageGeometry<Q, CPB, NW>;
@@ -457,6 +470,19 @@ MCFD_HD void StagePhaseC(const StageArgs &p, int tid, int bid, double *smem,
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
       const int id = d == 0 ? i0 : (d == 1 ? i1 : i2);
+      if (kGeneral) {
+        const int st = d == 0 ? FQ : (d == 1 ? Q : 1);
+        const int base = n - id * st;
+#pragma unroll
+        for (int side = 0; side < 2; ++side) {
+          const int e = base + (side ? (Q - 1) * st : 0);            // end node of my line
+          const int pt = FaceOf(d, side != 0) * FQ + c_tab.node_q[e][d];
+          const double gg = side ? -c_tab.g[1][id] : c_tab.g[0][id];   // -g' * sgn of that face
+#pragma unroll
+          for (int c = 0; c < 5; ++c) r[c] = fma(gg, g.sC[((size_t)pt * 5 + c) * CPB + lc], r[c]);
+        }
+        continue;
+      }
       const int q = c_tab.node_q[n][d];
       if (q < 0) continue;
       const int pt = FaceOf(d, id != 0) * FQ + q;
@@ -482,7 +508,7 @@ MCFD_HD void StagePhaseC(const StageArgs &p, int tid, int bid, double *smem,
 // One CTA-sized block, all phases; `sync` is __syncthreads() on the device and a no-op marker on the
 // host, where RunStageBlockOnHost() below replays the phases thread by thread.
 #ifdef __CUDACC__
-template <int Q, int kRiemann, int CPB, int NW>
+template <int Q, int kRiemann, int CPB, int NW, bool kGeneral>
 __global__ void __launch_bounds__(NW * 32, (Q == 3 ? MCFD_P2_MINB : 1))
 StageKernel(StageArgs p) {
   extern __shared__ double smem[];
@@ -494,19 +520,19 @@ StageKernel(StageArgs p) {
   __syncthreads();
   StagePhaseA<Q, CPB, NW>(p, tid, bid, smem, su, &res);
   __syncthreads();
-  StagePhaseB1<Q, CPB, NW>(p, tid, bid, smem, &res);
+  StagePhaseB1<Q, CPB, NW, kGeneral>(p, tid, bid, smem, &res);
   __syncthreads();
   StageStoreResiduals<Q, CPB, NW>(p, tid, bid, smem, res);
-  StagePhaseB2<Q, kRiemann, CPB, NW>(p, tid, bid, smem);
+  StagePhaseB2<Q, kRiemann, CPB, NW, kGeneral>(p, tid, bid, smem);
   // the states needed by the update are requested before the last barrier
   SlotStates<Q, CPB, NW> su0;
   StageLoadSlots<Q, CPB, NW>(p, tid, bid, smem, p.u_in, &su);
   StageLoadSlots<Q, CPB, NW>(p, tid, bid, smem, p.mode >= kModeRk3b ? p.u0 : p.u_in, &su0);
   __syncthreads();
-  StagePhaseC<Q, CPB, NW>(p, tid, bid, smem, su, su0, res);
+  StagePhaseC<Q, CPB, NW, kGeneral>(p, tid, bid, smem, su, su0, res);
 }
 #else
-template <int Q, int kRiemann, int CPB, int NW>
+template <int Q, int kRiemann, int CPB, int NW, bool kGeneral>
 void RunStageBlockOnHost(const StageArgs &p, int bid, double *smem) {
   constexpr int T = NW * 32;
   static SlotStates<Q, CPB, NW> su[T], su0[T];
@@ -516,13 +542,13 @@ void RunStageBlockOnHost(const StageArgs &p, int bid, double *smem) {
     StagePrologue<Q, CPB, NW>(p, t, bid, smem);
   }
   for (int t = 0; t < T; ++t) StagePhaseA<Q, CPB, NW>(p, t, bid, smem, su[t], &res[t]);
-  for (int t = 0; t < T; ++t) StagePhaseB1<Q, CPB, NW>(p, t, bid, smem, &res[t]);
+  for (int t = 0; t < T; ++t) StagePhaseB1<Q, CPB, NW, kGeneral>(p, t, bid, smem, &res[t]);
   for (int t = 0; t < T; ++t) StageStoreResiduals<Q, CPB, NW>(p, t, bid, smem, res[t]);
   for (int t = 0; t < T; ++t) {
-    StagePhaseB2<Q, kRiemann, CPB, NW>(p, t, bid, smem);
+    StagePhaseB2<Q, kRiemann, CPB, NW, kGeneral>(p, t, bid, smem);
     StageLoadSlots<Q, CPB, NW>(p, t, bid, smem, p.mode >= kModeRk3b ? p.u0 : p.u_in, &su0[t]);
   }
-  for (int t = 0; t < T; ++t) StagePhaseC<Q, CPB, NW>(p, t, bid, smem, su[t], su0[t], res[t]);
+  for (int t = 0; t < T; ++t) StagePhaseC<Q, CPB, NW, kGeneral>(p, t, bid, smem, su[t], su0[t], res[t]);
 }
 #endif
 

@@ -86,10 +86,10 @@ int Fail(mcfd_ctx *ctx, int status, std::string msg) {
       return Fail(ctx, MCFD_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
   } while (0)
 
-template <int Q, int R, int CPB, int NW>
-cudaError_t LaunchStageT(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
+template <int Q, int R, int CPB, int NW, bool kGeneral>
+cudaError_t LaunchStageG(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
   size_t smem = StageGeometry<Q, CPB, NW>::kSharedBytes;
-  auto kernel = StageKernel<Q, R, CPB, NW>;
+  auto kernel = StageKernel<Q, R, CPB, NW, kGeneral>;
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -98,6 +98,13 @@ cudaError_t LaunchStageT(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
   }
   kernel<<<n_blocks, NW * 32, smem, ctx->stream>>>(a);
   return cudaGetLastError();
+}
+
+// the general Vincent correction (fr::General) is a separate instantiation: the lumped schemes pay nothing
+template <int Q, int R, int CPB, int NW>
+cudaError_t LaunchStageT(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
+  return ctx->cfg.scheme == MCFD_FR_GENERAL ? LaunchStageG<Q, R, CPB, NW, true>(ctx, a, n_blocks)
+                                            : LaunchStageG<Q, R, CPB, NW, false>(ctx, a, n_blocks);
 }
 
 template <int Q, int CPB, int NW>
@@ -214,7 +221,7 @@ int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
   if (!config || !ctx_out) return Fail(nullptr, MCFD_ERR_ARG, "null argument");
   if (config->degree != 2 && config->degree != 3)
     return Fail(nullptr, MCFD_ERR_ARG, "degree must be 2 or 3");
-  if (config->scheme != MCFD_FR_LOBATTO && config->scheme != MCFD_DG_LOBATTO)
+  if (config->scheme < MCFD_FR_LOBATTO || config->scheme > MCFD_FR_GENERAL)
     return Fail(nullptr, MCFD_ERR_ARG, "unknown scheme");
   if (config->riemann < MCFD_EXACT || config->riemann > MCFD_AUSM)
     return Fail(nullptr, MCFD_ERR_ARG, "unknown Riemann solver");
@@ -235,7 +242,7 @@ int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
   ctx->fields = 5 * ctx->n_nodes;
   ctx->cpb = (ctx->q == 3) ? kP2Cells : kP3Cells;
   ctx->n_warps = (ctx->q == 3) ? kP2Warps : kP3Warps;
-  ctx->tables = BuildTables(config->degree, config->scheme, ctx->n_warps, kTile / ctx->cpb);
+  ctx->tables = BuildTables(config->degree, config->scheme, ctx->n_warps, kTile / ctx->cpb, config->fr_c_next);
   e = cudaMemcpyToSymbol(c_tab, &ctx->tables, sizeof(Tables));
   if (e != cudaSuccess) return Fail(nullptr, MCFD_ERR_CUDA, cudaGetErrorString(e));
   e = ctx->dt_bits.Alloc(1);
@@ -754,7 +761,7 @@ extern "C" {
 int mcfd_time_step_static(int32_t scheme, int32_t degree, int64_t n_cells, const double *column_dev,
     const double *length_dev, double dt_guess, int32_t rk_order, double *dt_dev, void *cuda_stream) {
   if (!column_dev || !length_dev || !dt_dev) return Fail(nullptr, MCFD_ERR_ARG, "mcfd_time_step_static: null pointer");
-  if ((degree != 2 && degree != 3) || (scheme != MCFD_FR_LOBATTO && scheme != MCFD_DG_LOBATTO) || rk_order < 0 || rk_order > 4)
+  if ((degree != 2 && degree != 3) || (scheme < MCFD_FR_LOBATTO || scheme > MCFD_FR_GENERAL) || rk_order < 0 || rk_order > 4)
     return Fail(nullptr, MCFD_ERR_ARG, "mcfd_time_step_static: unsupported scheme, degree or RK order");
   if (n_cells <= 0) return Fail(nullptr, MCFD_ERR_ARG, "mcfd_time_step_static: n_cells must be positive");
   if (n_cells > kStaticMaxCells)

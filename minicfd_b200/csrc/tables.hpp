@@ -66,6 +66,22 @@ inline double HuynhLumpedGPrimeAtOne(int degree) {
   return 0.5 * (curr + c_prev * prev + c_next * next);
 }
 
+inline double LegendreP(int k, double x) {   // std::legendre
+  double p0 = 1, p1 = x;
+  if (k == 0) return p0;
+  for (int n = 1; n < k; ++n) { double p2 = ((2 * n + 1) * x * p1 - n * p0) / (n + 1); p0 = p1; p1 = p2; }
+  return p1;
+}
+// Vincent::LocalToRightDerivative (basis/vincent.hpp:75-91) for a given c_next
+inline double VincentRightDerivative(int degree, double c_next, double local) {
+  double c_prev = 1 - c_next, prev = 0, curr = 0, next = 0;
+  for (int k = 0; k <= degree; ++k) {
+    if (k > 0) { prev = curr; curr = next; }
+    next = (k + 1) * LegendreP(k, local) + local * curr;
+  }
+  return 0.5 * (curr + c_prev * prev + c_next * next);
+}
+
 // Square symmetry o: my face corner m coincides with the neighbour's face corner pi(m);
 // o = pi(0) + 4*reversed, reversed <=> pi(1) == pi(0) - 1 (mod 4).
 inline int CornerImage(int o, int m) {
@@ -90,7 +106,7 @@ inline int FaceNode(int q, const double *x, int f, int ia, int ib) {
   return (i * q + j) * q + k;
 }
 
-inline Tables BuildTables(int degree, int scheme, int n_warps, int sub) {
+inline Tables BuildTables(int degree, int scheme, int n_warps, int sub, double c_next = 0.0) {
   Tables t{};
   const int q = degree + 1, n = q * q * q, fq = q * q;
   double x[kMaxQ], w[kMaxQ];
@@ -105,6 +121,14 @@ inline Tables BuildTables(int degree, int scheme, int n_warps, int sub) {
   }
   t.coef_f = (scheme == 0) ? g_prime : 1.0 / w[q - 1];
   t.coef_F = (scheme == 0) ? g_prime : 0.0;
+  t.general = scheme == 2;
+  if (scheme == 2) {   // fr::General: g'_left(xi) = -g'_right(-xi) (basis/vincent.hpp:99-101)
+    for (int i = 0; i < q; ++i) {
+      t.g[1][i] = VincentRightDerivative(degree, c_next, x[i]);
+      t.g[0][i] = -VincentRightDerivative(degree, c_next, -x[i]);
+      for (int m = 0; m < q; ++m) t.a[i][m] = -LagrangeDerivative(q, x, m, i);
+    }
+  }
   // face-point index of every cell node on each of its faces
   int face_node[6][kMaxFaceQ];
   for (int f = 0; f < 6; ++f)

@@ -15,10 +15,10 @@ from .part import Part, cell_points
 
 class Spatial:
     def __init__(self, part: Part, *, scheme=capi.FR_LOBATTO, degree=2, riemann=capi.HLLC, device=-1,
-                 comm=None):
+                 comm=None, fr_c_next=0.0):
         self.part = part
         self.degree = degree
-        self.ctx = capi.Context(scheme, degree, riemann, device)
+        self.ctx = capi.Context(scheme, degree, riemann, device, fr_c_next)
         self.kfields = self.ctx.kfields
         m = part.mesh
         self.ctx.set_mesh(m.nodes, part.cell_nodes, part.n_local, part.n_ghost, part.bfaces, part.btags,

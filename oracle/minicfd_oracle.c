@@ -360,8 +360,24 @@ static double g_prime_right_at_one(int degree) { /* basis/vincent.hpp:31-33, 75-
   return 0.5 * (curr + cp * prev + cn * next);
 }
 
+static double legendre_p(int k, double x) { /* std::legendre */
+  double p0 = 1, p1 = x;
+  if (k == 0) return p0;
+  for (int n = 1; n < k; ++n) { double p2 = ((2 * n + 1) * x * p1 - n * p0) / (n + 1); p0 = p1; p1 = p2; }
+  return p1;
+}
+static double vincent_right_derivative(int degree, double c_next, double x) { /* basis/vincent.hpp:75-91 */
+  double cp = 1 - c_next, prev = 0, curr = 0, next = 0;
+  for (int k = 0; k <= degree; ++k) {
+    if (k > 0) { prev = curr; curr = next; }
+    next = (k + 1) * legendre_p(k, x) + x * curr;
+  }
+  return 0.5 * (curr + cp * prev + c_next * next);
+}
+
 typedef struct {
-  int degree, q, n, scheme, riemann;
+  int degree, q, n, scheme, riemann;   /* scheme: 0 fr::Lobatto, 1 dg::Lobatto, 2 fr::General */
+  double c_next;                       /* fr::General only (fr/general.hpp:218-219) */
   int64_t n_cells;
   double x[MAXQ], w[MAXQ], d1[MAXQ][MAXQ]; /* d1[i][m] = l_m'(x_i) */
   double *xyz;      /* [cell][n][3] node coordinates */
@@ -550,6 +566,8 @@ void oracle_destroy(void *h) {
   free(o->s_scale); free(o->frame); free(o->fweight); free(o->fxyz); free(o);
 }
 
+void oracle_set_vincent(void *h, double c_next) { ((oracle_t *)h)->c_next = c_next; }
+
 void oracle_set_bc(void *h, int tag, int bc_kind, int field_kind, const double *prm) {
   oracle_t *o = h;
   o->bc_kind[tag] = bc_kind; o->field_kind[tag] = field_kind;
@@ -590,7 +608,7 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
         g[1] = (ia[0] == ib[0] && ia[2] == ib[2]) ? o->d1[ia[1]][ib[1]] : 0;
         g[2] = (ia[0] == ib[0] && ia[1] == ib[1]) ? o->d1[ia[2]][ib[2]] : 0;
         if (g[0] == 0 && g[1] == 0 && g[2] == 0) continue;
-        if (o->scheme == 0) { /* fr/general.hpp:280-286: res[a] -= Fhat_b . grad phi_b(xi_a) */
+        if (o->scheme != 1) { /* fr/general.hpp:280-286: res[a] -= Fhat_b . grad phi_b(xi_a) */
           const double *fh = &fhat[(c * n + b) * 15];
           for (int k = 0; k < 5; ++k)
             res[(c * n + a) * K + k] -= fh[k * 3] * g[0] + fh[k * 3 + 1] * g[1] + fh[k * 3 + 2] * g[2];
@@ -618,7 +636,25 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
       if (cs >= 0) {
         int as = o->s_node[f * fq + p];
         flux_upwind(o->riemann, fr, uh, &u[(cs * n + as) * K], fu);
-        if (o->scheme == 0) { /* fr/general.hpp:296-315, fr/lobatto.hpp:232-251 */
+        if (o->scheme == 2) { /* fr/general.hpp:296-315, 409-434: the whole node line is corrected */
+          double sh = o->h_scale[f * fq + p], ss = o->s_scale[f * fq + p];
+          const double *Fh = &fhat[(ch * n + ah) * 15], *Fs = &fhat[(cs * n + as) * 15];
+          int strd[3] = {fq, q, 1};
+          for (int side = 0; side < 2; ++side) {
+            int64_t cell = side ? cs : ch;
+            int a0 = side ? as : ah, d = side ? o->s_dir[f] : o->h_dir[f];
+            double scale = side ? ss : sh;
+            int id = (a0 / strd[d]) % q, base = a0 - id * strd[d];
+            for (int i = 0; i < q; ++i) { /* fr/general.hpp:113-119, 147-153: left or right derivative */
+              double gpr = scale > 0 ? vincent_right_derivative(o->degree, o->c_next, o->x[i])
+                                     : -vincent_right_derivative(o->degree, o->c_next, -o->x[i]);
+              for (int k = 0; k < 5; ++k) {
+                double fc = side ? fu[k] * (-ss) - Fs[k * 3 + d] : fu[k] * sh - Fh[k * 3 + d];
+                res[(cell * n + base + i * strd[d]) * K + k] -= fc * gpr;
+              }
+            }
+          }
+        } else if (o->scheme == 0) { /* fr/general.hpp:296-315, fr/lobatto.hpp:232-251 */
           double sh = o->h_scale[f * fq + p], ss = o->s_scale[f * fq + p];
           double gh = sh > 0 ? gp : -gp, gs = ss > 0 ? gp : -gp;
           const double *Fh = &fhat[(ch * n + ah) * 15], *Fs = &fhat[(cs * n + as) * 15];
@@ -640,7 +676,18 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
         double given[5] = {0, 0, 0, 0, 0};
         if (kind >= 2) eval_field(o->field_kind[tag], o->field_prm[tag], &o->fxyz[(f * fq + p) * 3], t, given);
         boundary_flux(o->riemann, kind, fr, uh, given, fu);
-        if (o->scheme == 0) { /* fr/lobatto.hpp:278-428 */
+        if (o->scheme == 2) { /* fr/general.hpp:435-640 */
+          double sh = o->h_scale[f * fq + p];
+          const double *Fh = &fhat[(ch * n + ah) * 15];
+          int strd[3] = {fq, q, 1}, d = o->h_dir[f];
+          int id = (ah / strd[d]) % q, base = ah - id * strd[d];
+          for (int i = 0; i < q; ++i) {
+            double gpr = sh > 0 ? vincent_right_derivative(o->degree, o->c_next, o->x[i])
+                                : -vincent_right_derivative(o->degree, o->c_next, -o->x[i]);
+            for (int k = 0; k < 5; ++k)
+              res[(ch * n + base + i * strd[d]) * K + k] -= (fu[k] * sh - Fh[k * 3 + d]) * gpr;
+          }
+        } else if (o->scheme == 0) { /* fr/lobatto.hpp:278-428 */
           double sh = o->h_scale[f * fq + p], gh = sh > 0 ? gp : -gp;
           const double *Fh = &fhat[(ch * n + ah) * 15];
           for (int k = 0; k < 5; ++k) res[(ch * n + ah) * K + k] -= (fu[k] * sh - Fh[k * 3 + o->h_dir[f]]) * gh;
@@ -654,7 +701,7 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
   for (int64_t c = 0; c < nc; ++c)
     for (int a = 0; a < n; ++a) {
       int ia[3] = {a / fq, (a / q) % q, a % q};
-      double s = o->scheme == 0 ? 1.0 / o->det[c * n + a] /* fr/general.hpp:256-266 */
+      double s = o->scheme != 1 ? 1.0 / o->det[c * n + a] /* fr/general.hpp:256-266 */
           : 1.0 / (o->w[ia[0]] * o->w[ia[1]] * o->w[ia[2]] * o->det[c * n + a]); /* dg/lobatto.hpp:143-158 */
       for (int k = 0; k < 5; ++k) res[(c * n + a) * K + k] *= s;
     }

@@ -551,7 +551,7 @@ struct SolverImpl : SolverBase {
   std::vector<std::unique_ptr<Spatial>> spatials;
   std::vector<Column> residuals;
 
-  explicit SolverImpl(GlobalMesh &&m) : mesh(std::move(m)) {
+  explicit SolverImpl(GlobalMesh &&m, double c_next = 0.0) : mesh(std::move(m)) {
     mesh.Build();
     comm = std::make_unique<InProcessComm>(mesh.n_parts);
     parts.resize(mesh.n_parts);
@@ -560,8 +560,12 @@ struct SolverImpl : SolverBase {
     ForEachPart([this](int r) {
       parts[r] = std::make_unique<Part>(&mesh, comm.get(), r);
     });
-    ForEachPart([this](int r) {
-      spatials[r] = std::make_unique<Spatial>(parts[r].get());
+    ForEachPart([this, c_next](int r) {
+      if constexpr (std::is_constructible_v<Spatial, Part *, Scalar>) {
+        spatials[r] = std::make_unique<Spatial>(parts[r].get(), c_next);   // fr::General(part, c_next)
+      } else {
+        spatials[r] = std::make_unique<Spatial>(parts[r].get());
+      }
     });
   }
   template <class F>
@@ -679,6 +683,9 @@ using RExact = Rotated<mini::riemann::euler::Exact<Gas, 3>>;
 using RHllc = Rotated<mini::riemann::euler::HartenLaxLeerContact<Gas, 3>>;
 using RAusm = Rotated<mini::riemann::euler::AdvectionUpstreamSplittingMethod<Gas, 3>>;
 
+// c_next of the next fr::General to be created (fr/general.hpp:218-219); set by ref_pN_set_vincent
+static double g_c_next = 0.0;
+
 static SolverBase *Create(int scheme, int riemann, GlobalMesh &&mesh) {
   namespace sp = mini::spatial;
   if (scheme == 0) {
@@ -692,6 +699,12 @@ static SolverBase *Create(int scheme, int riemann, GlobalMesh &&mesh) {
     case 0: return new SolverImpl<sp::dg::Lobatto<Part, RExact>>(std::move(mesh));
     case 1: return new SolverImpl<sp::dg::Lobatto<Part, RHllc>>(std::move(mesh));
     case 2: return new SolverImpl<sp::dg::Lobatto<Part, RAusm>>(std::move(mesh));
+    }
+  } else if (scheme == 2) {
+    switch (riemann) {
+    case 0: return new SolverImpl<sp::fr::General<Part, RExact>>(std::move(mesh), g_c_next);
+    case 1: return new SolverImpl<sp::fr::General<Part, RHllc>>(std::move(mesh), g_c_next);
+    case 2: return new SolverImpl<sp::fr::General<Part, RAusm>>(std::move(mesh), g_c_next);
     }
   }
   return nullptr;
@@ -713,6 +726,8 @@ using oracle::SolverBase;
 extern "C" {
 
 int REF_FN(degree)() { return REF_DEGREE; }
+
+void REF_FN(set_vincent)(double c_next) { oracle::g_c_next = c_next; }
 
 void *REF_FN(create)(int scheme, int riemann, Int n_nodes, const double *xyz, Int n_cells,
     const Int *cell_nodes, const int *cell_parts, int n_parts, Int n_bfaces,

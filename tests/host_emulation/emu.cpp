@@ -19,7 +19,10 @@ template <int Q, int R, int CPB, int NW>
 void RunStage(StageArgs a, int n_blocks) {
   using G = StageGeometry<Q, CPB, NW>;
   std::vector<double> smem(G::kSharedBytes / sizeof(double) + 1);
-  for (int b = 0; b < n_blocks; ++b) RunStageBlockOnHost<Q, R, CPB, NW>(a, b, smem.data());
+  for (int b = 0; b < n_blocks; ++b) {
+    if (c_tab.general) RunStageBlockOnHost<Q, R, CPB, NW, true>(a, b, smem.data());
+    else RunStageBlockOnHost<Q, R, CPB, NW, false>(a, b, smem.data());
+  }
 }
 
 template <int Q, int CPB, int NW>
@@ -48,10 +51,10 @@ int emu_stage(int degree, int scheme, int riemann, int64_t n_nodes, const double
     int64_t n_local, int64_t n_ghost, const int64_t *cell_nodes, int64_t n_bfaces,
     const int64_t *bface_nodes, const int32_t *bface_tags, int64_t n_pairs, const int64_t *pairs,
     const int32_t *tag_kinds, const double *bvals, const double *column_in, const double *column_u0,
-    int mode, double dt, double *column_out, char *err, int err_len) {
+    int mode, double dt, double *column_out, char *err, int err_len, double c_next) {
   const int q = degree + 1, F = 5 * q * q * q;
   const int cpb = (q == 3) ? kP2Cells : kP3Cells, nw = (q == 3) ? kP2Warps : kP3Warps;
-  c_tab = BuildTables(degree, scheme, nw, kTile / cpb);
+  c_tab = BuildTables(degree, scheme, nw, kTile / cpb, c_next);
   HostMesh mesh;
   if (!mesh.Build(degree, n_nodes, xyz, n_local, n_ghost, cell_nodes, n_bfaces, bface_nodes,
           bface_tags, n_pairs, pairs)) {

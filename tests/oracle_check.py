@@ -33,7 +33,7 @@ def _dp(a):
 
 
 class Oracle:
-    def __init__(self, mesh, degree=2, scheme=0, riemann=1):
+    def __init__(self, mesh, degree=2, scheme=0, riemann=1, c_next=0.0):
         nodes = np.ascontiguousarray(mesh.nodes, dtype=np.float64)
         cells = np.ascontiguousarray(mesh.cells, dtype=np.int64)
         bf = np.ascontiguousarray(mesh.bfaces, dtype=np.int64)
@@ -44,6 +44,7 @@ class Oracle:
             C.c_int(degree), C.c_int(scheme), C.c_int(riemann), C.c_int64(len(nodes)), _dp(nodes),
             C.c_int64(len(cells)), cells.ctypes.data_as(C.POINTER(C.c_int64)), C.c_int64(len(bf)),
             bf.ctypes.data_as(C.POINTER(C.c_int64)), bt.ctypes.data_as(C.POINTER(C.c_int32))))
+        lib().oracle_set_vincent(self.h, C.c_double(c_next))
 
     def __del__(self):
         try:

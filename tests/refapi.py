@@ -12,7 +12,7 @@ _libs: dict[int, C.CDLL] = {}
 
 CB = C.CFUNCTYPE(None, C.c_int, C.POINTER(C.c_double), C.c_double, C.POINTER(C.c_double), C.c_void_p)
 
-FR, DG = 0, 1
+FR, DG, FR_GENERAL = 0, 1, 2
 EXACT, HLLC, AUSM = 0, 1, 2
 # boundary kinds, order of fem.hpp:196-222 as used by ref_harness.cpp
 WALL, SUPERSONIC_OUTLET, SUPERSONIC_INLET, SUBSONIC_INLET, SUBSONIC_OUTLET, SMART = range(6)
@@ -41,7 +41,7 @@ def _i32(a):
 
 
 class Ref:
-    def __init__(self, mesh, degree=2, scheme=FR, riemann=HLLC, cell_parts=None, n_parts=1):
+    def __init__(self, mesh, degree=2, scheme=FR, riemann=HLLC, cell_parts=None, n_parts=1, c_next=0.0):
         if degree not in _libs:
             _libs[degree] = C.CDLL(lib_path(degree))
         self.lib = _libs[degree]
@@ -49,6 +49,7 @@ class Ref:
         self.pre = f"ref_p{degree}_"
         self.n_nodes_per_cell = (degree + 1) ** 3
         self.kfields = 5 * self.n_nodes_per_cell
+        self._f("set_vincent")(C.c_double(c_next))
         f = self._f("create")
         f.restype = C.c_void_p
         nodes = np.ascontiguousarray(mesh.nodes, dtype=np.float64)

@@ -324,3 +324,20 @@ def test_initial_limiters(degree, kind):
         assert np.array_equal(got, expect)          # pure selection: bit-exact
     else:
         assert relerr(got, expect) < TOL
+
+
+@pytest.mark.parametrize("degree,c_next,riemann", [(2, 1.0, capi.HLLC), (2, 0.3, capi.EXACT), (3, 0.8, capi.AUSM)])
+def test_fr_general_vincent(degree, c_next, riemann):
+    """fr::General(part, c_next) (SURVEY row a10): residual, time step (no doubling) and RK3 vs the oracle."""
+    m = cases.small_mesh(seed=8)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), seed=2)
+    o = oc.Oracle(m, degree, 2, riemann, c_next=c_next)
+    cases.apply_bcs_oracle(o)
+    sp = Spatial(Part(m), scheme=capi.FR_GENERAL, degree=degree, riemann=riemann, device=0, fr_c_next=c_next)
+    cases.apply_bcs_spatial(sp, cases.MIXED_BCS)
+    sp.SetSolutionColumn(u)
+    sp.SetTime(0.2)
+    assert relerr(sp.GetResidualColumn(), o.residual(u, 0.2)) < TOL
+    assert sp.GetTimeStep(1.0, 3) == pytest.approx(o.time_step(u, 1.0, 3), rel=1e-13)
+    RungeKutta(3).Update(sp, 0.0, 1e-3)
+    assert relerr(sp.GetSolutionColumn(), o.rk_update(u, 3, 0.0, 1e-3)) < TOL

@@ -177,3 +177,18 @@ def test_halo_exchange_two_gloo_ranks(tmp_path):
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stdout + out.stderr
     assert out.stdout.count("OK") == 2
+
+
+@pytest.mark.parametrize("degree,c_next", [(2, 1.0), (3, 0.3)])
+def test_kernel_source_fr_general(degree, c_next):
+    """General Vincent correction in the kernel source vs the oracle, mixed boundaries."""
+    m = cases.small_mesh(seed=8)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), seed=2)
+    o = oc.Oracle(m, degree, 2, 1, c_next=c_next)
+    cases.apply_bcs_oracle(o)
+    holder, hf, tags, pts = emuapi.boundary(m, degree)
+    bvals = np.zeros(pts.shape[:2] + (5,))
+    for tag, kind in cases.MIXED_BCS.items():
+        bvals[tags == tag] = cases.bc_function(kind)(pts[tags == tag], 0.2)
+    got = emuapi.stage(m, degree, 2, 1, u, tag_kinds=cases.MIXED_BCS, bvals=bvals, c_next=c_next)
+    assert relerr(got, o.residual(u, 0.2)) < 1e-12

@@ -155,3 +155,26 @@ def test_initial_limiters_match_reference(degree, kind):
     o = oc.Oracle(m, degree)
     got, ref = o.limiter(u, kind), r.get_solution()
     assert np.abs(got - ref).max() <= 1e-14 * np.abs(ref).max()
+
+
+@pytest.mark.skipif(not refapi.available(2), reason="oracle/_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("degree,c_next", [(2, 1.0), (2, 0.3), (3, 3.0 / 7), (3, 0.8)])
+def test_c_oracle_fr_general_matches_reference(degree, c_next):
+    """fr::General with an arbitrary Vincent c (fr/general.hpp; c = P/(2P+1) must equal fr::Lobatto,
+    the cross-check of test/spatial/fr.cpp:82-97)."""
+    m = cases.small_mesh(seed=8)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), seed=2)
+    r = refapi.Ref(m, degree=degree, scheme=refapi.FR_GENERAL, riemann=refapi.AUSM, c_next=c_next)
+    o = oc.Oracle(m, degree, 2, 2, c_next=c_next)
+    cases.apply_bcs_ref(r)
+    cases.apply_bcs_oracle(o)
+    r.set_solution(u)
+    ref = r.residual(0.2)
+    assert relerr(o.residual(u, 0.2), ref) < TOL
+    assert o.time_step(u, 1.0, 3) == r.time_step(1.0, 3)          # no FR-Lobatto doubling
+    r.rk_update(3, 0.0, 1e-3, 1)
+    assert relerr(o.rk_update(u, 3, 0.0, 1e-3), r.get_solution()) < TOL
+    if abs(c_next - degree / (2.0 * degree + 1)) < 1e-15:          # Huynh's lumping value
+        lob = oc.Oracle(m, degree, 0, 2)
+        cases.apply_bcs_oracle(lob)
+        assert relerr(lob.residual(u, 0.2), ref) < 1e-13
