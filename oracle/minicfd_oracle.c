@@ -351,6 +351,19 @@ static double lagrange_d(int q, const double *x, int m, int i) { /* l_m'(x_i), b
   }
   return sum;
 }
+static double lagrange_d2(int q, const double *x, int m, int i) { /* l_m''(x_i), basis/lagrange.hpp:130-133 with k = 2 */
+  double sum = 0;
+  for (int k = 0; k < q; ++k) {
+    if (k == m) continue;
+    for (int j = 0; j < q; ++j) {
+      if (j == m || j == k) continue;
+      double prod = 1.0 / ((x[m] - x[k]) * (x[m] - x[j]));
+      for (int l = 0; l < q; ++l) if (l != m && l != k && l != j) prod *= (x[i] - x[l]) / (x[m] - x[l]);
+      sum += prod;
+    }
+  }
+  return sum;
+}
 static double g_prime_right_at_one(int degree) { /* basis/vincent.hpp:31-33, 75-91 */
   double cn = degree / (2.0 * degree + 1), cp = 1 - cn, prev = 0, curr = 0, next = 0;
   for (int k = 0; k <= degree; ++k) {
@@ -376,7 +389,12 @@ static double vincent_right_derivative(int degree, double c_next, double x) { /*
 }
 
 typedef struct {
-  int degree, q, n, scheme, riemann;   /* scheme: 0 fr::Lobatto, 1 dg::Lobatto, 2 fr::General */
+  int degree, q, n, scheme, riemann;   /* scheme: 0 fr::Lobatto, 1 dg::Lobatto, 2 fr::General,
+                                          3 fr::Lobatto on ConvectionDiffusion<Euler, Direct<NavierStokes>> */
+  double beta0, beta1, nu, prandtl;    /* direct.hpp:31-32, navier_stokes.hpp:54 (class statics there) */
+  double d2[MAXQ][MAXQ];               /* d2[i][m] = l_m''(x_i) */
+  double *jtgrad;   /* [cell][n][3][3][3] d(J^-T)/d(xi_a) = mat_after_grad_of_U_, hexahedron.hpp:233-236 */
+  double *dist;     /* [face][q*q] normal . HolderToSharer, fem.hpp:83-85 */
   double c_next;                       /* fr::General only (fr/general.hpp:218-219) */
   int64_t n_cells;
   double x[MAXQ], w[MAXQ], d1[MAXQ][MAXQ]; /* d1[i][m] = l_m'(x_i) */
@@ -454,20 +472,28 @@ void *oracle_create(int degree, int scheme, int riemann, int64_t n_nodes, const 
   o->jinv = malloc(sizeof(double) * n_cells * n * 9);
   o->det = malloc(sizeof(double) * n_cells * n);
   o->length = malloc(sizeof(double) * n_cells);
+  o->jtgrad = malloc(sizeof(double) * n_cells * n * 27);
+  for (int i = 0; i < q; ++i) for (int m = 0; m < q; ++m) o->d2[i][m] = lagrange_d2(q, o->x, m, i);
+  o->beta0 = 2.0; o->beta1 = 1.0 / 12; o->nu = 0.0; o->prandtl = 0.708;
   for (int64_t c = 0; c < n_cells; ++c) {
     double vol = 0;
     for (int a = 0; a < n; ++a) {
       int ijk[3] = {a / fq, (a / q) % q, a % q};
       double loc[3] = {o->x[ijk[0]], o->x[ijk[1]], o->x[ijk[2]]};
-      double X[3] = {0, 0, 0}, J[3][3] = {{0}};
+      double X[3] = {0, 0, 0}, J[3][3] = {{0}}, dJ[3][3][3] = {{{0}}}; /* dJ[a] = dJ/dxi_a, coordinate/cell.hpp:100-119 */
       for (int v = 0; v < 8; ++v) { /* coordinate/hexahedron.hpp:413-456 */
         const double *P = &nodes[cn[c * 8 + v] * 3];
         double fx = 1 + VERT[v][0] * loc[0], fy = 1 + VERT[v][1] * loc[1], fz = 1 + VERT[v][2] * loc[2];
         double shape = fx * fy * fz / 8;
         double g[3] = {VERT[v][0] * (fy * fz / 8), VERT[v][1] * (fz * fx / 8), VERT[v][2] * (fx * fy / 8)};
+        double h01 = VERT[v][0] * VERT[v][1] * (fz / 8), h02 = VERT[v][0] * VERT[v][2] * (fy / 8);
+        double h12 = VERT[v][1] * VERT[v][2] * (fx / 8); /* shape Hessian; the diagonal vanishes for Hexahedron8 */
         for (int k = 0; k < 3; ++k) {
           X[k] += shape * P[k];
           for (int d = 0; d < 3; ++d) J[d][k] += g[d] * P[k]; /* J rows = local directions */
+          dJ[0][1][k] += h01 * P[k]; dJ[1][0][k] += h01 * P[k];
+          dJ[0][2][k] += h02 * P[k]; dJ[2][0][k] += h02 * P[k];
+          dJ[1][2][k] += h12 * P[k]; dJ[2][1][k] += h12 * P[k];
         }
       }
       memcpy(&o->xyz[(c * n + a) * 3], X, sizeof X);
@@ -480,6 +506,19 @@ void *oracle_create(int degree, int scheme, int riemann, int64_t n_nodes, const 
       }
       for (int k = 0; k < 9; ++k) js[k] = det * inv[k]; /* polynomial/hexahedron.hpp:228-230 */
       o->det[c * n + a] = det;
+      for (int e = 0; e < 3; ++e) { /* -(J^-1 dJ_e J^-1)^T, polynomial/hexahedron.hpp:233-236 */
+        double t1[3][3], t2[3][3];
+        for (int r = 0; r < 3; ++r) for (int s2 = 0; s2 < 3; ++s2) {
+          t1[r][s2] = 0;
+          for (int m = 0; m < 3; ++m) t1[r][s2] += inv[r * 3 + m] * dJ[e][m][s2];
+        }
+        for (int r = 0; r < 3; ++r) for (int s2 = 0; s2 < 3; ++s2) {
+          t2[r][s2] = 0;
+          for (int m = 0; m < 3; ++m) t2[r][s2] += t1[r][m] * inv[m * 3 + s2];
+        }
+        for (int r = 0; r < 3; ++r) for (int s2 = 0; s2 < 3; ++s2)
+          o->jtgrad[((c * n + a) * 3 + e) * 9 + s2 * 3 + r] = -t2[r][s2];
+      }
       vol += o->w[ijk[0]] * o->w[ijk[1]] * o->w[ijk[2]] * det; /* integrator/element.hpp:101-114 */
     }
     o->length[c] = cbrt(vol) * 0.5; /* mesh/part.hpp:230 */
@@ -525,6 +564,7 @@ void *oracle_create(int degree, int scheme, int riemann, int64_t n_nodes, const 
   o->frame = malloc(sizeof(frame_t) * nf * fq);
   o->fweight = malloc(sizeof(double) * nf * fq);
   o->fxyz = malloc(sizeof(double) * nf * fq * 3);
+  o->dist = malloc(sizeof(double) * nf * fq);
   for (int64_t f = 0; f < nf; ++f) {
     /* face quad in the holder's outward order (coordinate/cell.hpp:220-258) */
     const double *P[4];
@@ -550,6 +590,18 @@ void *oracle_create(int degree, int scheme, int riemann, int64_t n_nodes, const 
       double aa = Ja[0] * Ja[0] + Ja[1] * Ja[1] + Ja[2] * Ja[2], bb = Jb[0] * Jb[0] + Jb[1] * Jb[1] + Jb[2] * Jb[2];
       double ab = Ja[0] * Jb[0] + Ja[1] * Jb[1] + Ja[2] * Jb[2];
       o->fweight[f * fq + p] = o->w[ia] * o->w[ib] * sqrt(aa * bb - ab * ab);
+      /* HolderToSharer between the images of the local origins (mesh/part.hpp:118-133,
+         coordinate/hexahedron.hpp:45, quadrangle.hpp:44); distance of fem.hpp:83-85 */
+      double ch[3] = {0, 0, 0}, cs[3] = {0, 0, 0};
+      for (int v = 0; v < 8; ++v) for (int k = 0; k < 3; ++k) ch[k] += nodes[cn[o->holder[f] * 8 + v] * 3 + k] / 8;
+      if (o->sharer[f] >= 0) {
+        for (int v = 0; v < 8; ++v) for (int k = 0; k < 3; ++k) cs[k] += nodes[cn[o->sharer[f] * 8 + v] * 3 + k] / 8;
+        for (int k = 0; k < 3; ++k) cs[k] -= ch[k];
+      } else {
+        for (int m = 0; m < 4; ++m) for (int k = 0; k < 3; ++k) cs[k] += P[m][k] / 4;
+        for (int k = 0; k < 3; ++k) cs[k] = (cs[k] - ch[k]) * 2;
+      }
+      o->dist[f * fq + p] = fr->a[0] * cs[0] + fr->a[1] * cs[1] + fr->a[2] * cs[2];
     }
     match_side(o, o->holder[f], hface[f], &o->fxyz[f * fq * 3], &o->h_node[f * fq], &o->h_dir[f], &o->h_scale[f * fq]);
     if (o->sharer[f] >= 0)
@@ -561,12 +613,16 @@ void *oracle_create(int degree, int scheme, int riemann, int64_t n_nodes, const 
 
 void oracle_destroy(void *h) {
   oracle_t *o = h;
-  free(o->xyz); free(o->jstar); free(o->jinv); free(o->det); free(o->length); free(o->holder); free(o->sharer);
+  free(o->jtgrad); free(o->dist); free(o->xyz); free(o->jstar); free(o->jinv); free(o->det); free(o->length); free(o->holder); free(o->sharer);
   free(o->tag); free(o->h_node); free(o->s_node); free(o->h_dir); free(o->s_dir); free(o->h_scale);
   free(o->s_scale); free(o->frame); free(o->fweight); free(o->fxyz); free(o);
 }
 
 void oracle_set_vincent(void *h, double c_next) { ((oracle_t *)h)->c_next = c_next; }
+void oracle_set_viscous(void *h, double beta0, double beta1, double nu, double prandtl) {
+  oracle_t *o = h;
+  o->beta0 = beta0; o->beta1 = beta1; o->nu = nu; o->prandtl = prandtl;
+}
 
 void oracle_set_bc(void *h, int tag, int bc_kind, int field_kind, const double *prm) {
   oracle_t *o = h;
@@ -583,6 +639,154 @@ void oracle_approximate(void *h, int field_kind, const double *prm, double *colu
 
 /* FiniteElement::GetResidualColumn (fem.hpp:248-258) with fr/general.hpp:249-288, fr/lobatto.hpp:232-428
  * or dg/lobatto.hpp:143-302 */
+/* ---- viscous part: ConvectionDiffusion<rotated::Euler<..>, Direct<NavierStokes<Gas>>> ---------------- */
+/* gradients are [direction x,y,z][component], Hessians [XX,XY,XZ,YY,YZ,ZZ][component] (constant/index.hpp) */
+static void basis_local_gradient(const oracle_t *o, int a, int b, double g[3]) { /* hexahedron.hpp:142-153 */
+  int q = o->q, fq = q * q;
+  int ia[3] = {a / fq, (a / q) % q, a % q}, ib[3] = {b / fq, (b / q) % q, b % q};
+  g[0] = (ia[1] == ib[1] && ia[2] == ib[2]) ? o->d1[ia[0]][ib[0]] : 0;
+  g[1] = (ia[0] == ib[0] && ia[2] == ib[2]) ? o->d1[ia[1]][ib[1]] : 0;
+  g[2] = (ia[0] == ib[0] && ia[1] == ib[1]) ? o->d1[ia[2]][ib[2]] : 0;
+}
+static void basis_local_hessian(const oracle_t *o, int a, int b, double h[6]) { /* hexahedron.hpp:155-170 */
+  int q = o->q, fq = q * q;
+  int ia[3] = {a / fq, (a / q) % q, a % q}, ib[3] = {b / fq, (b / q) % q, b % q};
+  double v[3] = {ia[0] == ib[0], ia[1] == ib[1], ia[2] == ib[2]}; /* l_b(x_a) on each line */
+  double d[3] = {o->d1[ia[0]][ib[0]], o->d1[ia[1]][ib[1]], o->d1[ia[2]][ib[2]]};
+  double dd[3] = {o->d2[ia[0]][ib[0]], o->d2[ia[1]][ib[1]], o->d2[ia[2]][ib[2]]};
+  h[0] = dd[0] * v[1] * v[2]; h[1] = d[0] * d[1] * v[2]; h[2] = d[0] * v[1] * d[2];
+  h[3] = v[0] * dd[1] * v[2]; h[4] = v[0] * d[1] * d[2]; h[5] = v[0] * v[1] * dd[2];
+}
+/* Hexahedron::GetGlobalValueGradient for kLocal == false (hexahedron.hpp:479-486, 221-226) */
+static void global_gradient(const oracle_t *o, const double *u, int64_t c, int a, double g[3][5]) {
+  int n = o->n;
+  const double *inv = &o->jinv[(c * n + a) * 9];
+  memset(g, 0, sizeof(double) * 15);
+  for (int b = 0; b < n; ++b) {
+    double lg[3], gg[3];
+    basis_local_gradient(o, a, b, lg);
+    if (lg[0] == 0 && lg[1] == 0 && lg[2] == 0) continue;
+    for (int x = 0; x < 3; ++x) gg[x] = inv[x * 3] * lg[0] + inv[x * 3 + 1] * lg[1] + inv[x * 3 + 2] * lg[2];
+    for (int x = 0; x < 3; ++x) for (int k = 0; k < 5; ++k) g[x][k] += gg[x] * u[(c * n + b) * 5 + k];
+  }
+}
+/* Hexahedron::GetGlobalValueGradientHessian for kLocal == false (hexahedron.hpp:586-594, 496-524) */
+static void global_gradient_hessian(const oracle_t *o, const double *u, int64_t c, int a, double g[3][5],
+    double H[6][5]) {
+  int n = o->n;
+  const double *inv = &o->jinv[(c * n + a) * 9], *tg = &o->jtgrad[(c * n + a) * 27];
+  double lg[3][5], lh[6][5];
+  memset(lg, 0, sizeof lg); memset(lh, 0, sizeof lh);
+  for (int b = 0; b < n; ++b) {
+    double bg[3], bh[6];
+    basis_local_gradient(o, a, b, bg); basis_local_hessian(o, a, b, bh);
+    for (int k = 0; k < 5; ++k) {
+      double ub = u[(c * n + b) * 5 + k];
+      for (int x = 0; x < 3; ++x) lg[x][k] += bg[x] * ub;
+      for (int x = 0; x < 6; ++x) lh[x][k] += bh[x] * ub;
+    }
+  }
+  for (int x = 0; x < 3; ++x) for (int k = 0; k < 5; ++k)
+    g[x][k] = inv[x * 3] * lg[0][k] + inv[x * 3 + 1] * lg[1][k] + inv[x * 3 + 2] * lg[2][k];
+  static const int SYM[3][3] = {{0, 1, 2}, {1, 3, 4}, {2, 4, 5}};
+  for (int k = 0; k < 5; ++k) {
+    double S[3][3], G[3][3];
+    for (int e = 0; e < 3; ++e) for (int j = 0; j < 3; ++j) {
+      double v = 0;
+      for (int b = 0; b < 3; ++b) v += lh[SYM[e][b]][k] * inv[j * 3 + b];   /* scalar_hess *= J^-T */
+      for (int b = 0; b < 3; ++b) v += lg[b][k] * tg[e * 9 + b * 3 + j];    /* row(e) += grad^T d(J^-T)/dxi_e */
+      S[e][j] = v;
+    }
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j)
+      G[i][j] = inv[i * 3] * S[0][j] + inv[i * 3 + 1] * S[1][j] + inv[i * 3 + 2] * S[2][j];
+    H[0][k] = G[0][0]; H[1][k] = G[0][1]; H[2][k] = G[0][2]; H[3][k] = G[1][1]; H[4][k] = G[1][2]; H[5][k] = G[2][2];
+  }
+}
+/* NavierStokes::ConservativeToPrimitive (navier_stokes.hpp:91-125); column 4 of gp is grad T */
+static prim_t ns_primitive_gradient(const double *c, const double gc[3][5], double gp[3][5], double gpress[3]) {
+  prim_t q = cons_to_prim(c);
+  for (int x = 0; x < 3; ++x) {
+    gp[x][0] = gc[x][0];
+    gp[x][1] = (gc[x][1] - q.u * gc[x][0]) / q.rho;
+    gp[x][2] = (gc[x][2] - q.v * gc[x][0]) / q.rho;
+    gp[x][3] = (gc[x][3] - q.w * gc[x][0]) / q.rho;
+    double v = q.u * gc[x][1] + c[1] * gp[x][1];
+    v += q.v * gc[x][2] + c[2] * gp[x][2];
+    v += q.w * gc[x][3] + c[3] * gp[x][3];
+    v *= -0.5;
+    v += gc[x][4];
+    v *= (GAMMA - 1);
+    gpress[x] = v;
+    gp[x][4] = (v / q.rho - (q.p / (q.rho * q.rho)) * gc[x][0]) / GAS_R;
+  }
+  return q;
+}
+static void ns_stress(const double gp[3][5], double rho, double nu, double tau[6]) { /* :127-142, :70-74 */
+  double div = gp[0][1] + gp[1][2] + gp[2][3], mu = nu * rho, zeta = -2.0 / 3 * mu;
+  tau[0] = 2 * mu * gp[0][1] + zeta * div;
+  tau[3] = 2 * mu * gp[1][2] + zeta * div;
+  tau[5] = 2 * mu * gp[2][3] + zeta * div;
+  tau[1] = mu * (gp[1][1] + gp[0][2]);
+  tau[4] = mu * (gp[2][2] + gp[1][3]);
+  tau[2] = mu * (gp[0][3] + gp[2][1]);
+}
+static double ns_kappa(const oracle_t *o, double rho) { /* :76-79; Cp = R gamma/(gamma-1), types.hpp:245 */
+  return o->nu * rho * (GAS_R * (GAMMA / (GAMMA - 1))) / o->prandtl;
+}
+static void ns_minus_flux_matrix(const oracle_t *o, double F[5][3], const double *c, const double gc[3][5]) { /* :150-175 */
+  double gp[3][5], gpr[3], tau[6];
+  prim_t q = ns_primitive_gradient(c, gc, gp, gpr);
+  ns_stress(gp, c[0], o->nu, tau);
+  double kappa = ns_kappa(o, c[0]);
+  static const int SYM[3][3] = {{0, 1, 2}, {1, 3, 4}, {2, 4, 5}};
+  for (int x = 0; x < 3; ++x) {
+    F[4][x] -= kappa * gp[x][4];
+    F[1][x] -= tau[SYM[x][0]]; F[2][x] -= tau[SYM[x][1]]; F[3][x] -= tau[SYM[x][2]];
+    F[4][x] -= tau[SYM[x][0]] * q.u + tau[SYM[x][1]] * q.v + tau[SYM[x][2]] * q.w;
+  }
+}
+static void ns_minus_flux_core(const oracle_t *o, double *f, double rho, const double gp[3][5], const double *nrm,
+    const double *uvw, double n_dot_grad_t) { /* :178-190 */
+  double tau[6];
+  ns_stress(gp, rho, o->nu, tau);
+  static const int SYM[3][3] = {{0, 1, 2}, {1, 3, 4}, {2, 4, 5}};
+  double work[3];
+  for (int x = 0; x < 3; ++x) {
+    f[1 + x] -= tau[SYM[x][0]] * nrm[0] + tau[SYM[x][1]] * nrm[1] + tau[SYM[x][2]] * nrm[2];
+    work[x] = tau[SYM[x][0]] * uvw[0] + tau[SYM[x][1]] * uvw[1] + tau[SYM[x][2]] * uvw[2];
+  }
+  f[4] -= (work[0] * nrm[0] + work[1] * nrm[1] + work[2] * nrm[2]) + ns_kappa(o, rho) * n_dot_grad_t;
+}
+static void ns_minus_flux_normal(const oracle_t *o, double *f, const double *c, const double gc[3][5],
+    const double *nrm) { /* :193-202 */
+  double gp[3][5], gpr[3];
+  prim_t q = ns_primitive_gradient(c, gc, gp, gpr);
+  double uvw[3] = {q.u, q.v, q.w};
+  ns_minus_flux_core(o, f, c[0], gp, nrm, uvw, nrm[0] * gp[0][4] + nrm[1] * gp[1][4] + nrm[2] * gp[2][4]);
+}
+static void ns_minus_flux_no_slip(const oracle_t *o, double *f, const double *wall, const double *c,
+    const double gc[3][5], const double *nrm, double value_penalty) { /* :204-224 */
+  double gp[3][5], gpr[3];
+  prim_t q = ns_primitive_gradient(c, gc, gp, gpr);
+  double pen[3] = {value_penalty * (wall[1] - q.u), value_penalty * (wall[2] - q.v), value_penalty * (wall[3] - q.w)};
+  for (int x = 0; x < 3; ++x) for (int k = 0; k < 3; ++k) gp[x][1 + k] += nrm[x] * pen[k];
+  ns_minus_flux_core(o, f, c[0], gp, nrm, &wall[1], wall[4]);
+}
+/* Direct::GetCommonGradient with the Hessian penalty (direct.hpp:45-78, 85-90) */
+static void ddg_common_gradient(const oracle_t *o, double dist, const double *nrm, const double *ul, const double *ur,
+    const double gl[3][5], const double gr[3][5], const double hl[6][5], const double hr[6][5], double gc[3][5]) {
+  static const int SYM[3][3] = {{0, 1, 2}, {1, 3, 4}, {2, 4, 5}};
+  double n0[3], n1[3];
+  for (int x = 0; x < 3; ++x) { n0[x] = nrm[x] * (o->beta0 / dist); n1[x] = nrm[x] * (o->beta1 * dist); }
+  for (int x = 0; x < 3; ++x) for (int k = 0; k < 5; ++k) {
+    double v = (gl[x][k] + gr[x][k]) / 2;
+    v += n0[x] * (ur[k] - ul[k]);
+    gc[x][k] = v;
+  }
+  for (int x = 0; x < 3; ++x) for (int y = 0; y < 3; ++y) for (int k = 0; k < 5; ++k)
+    gc[x][k] += n1[y] * (hr[SYM[x][y]][k] - hl[SYM[x][y]][k]);
+}
+
 void oracle_residual(void *h, double t, const double *u, double *res) {
   oracle_t *o = h;
   int q = o->q, n = o->n, fq = q * q, K = 5;
@@ -593,6 +797,11 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
     for (int a = 0; a < n; ++a) {
       double F[5][3];
       flux_matrix(&u[(c * n + a) * K], F);
+      if (o->scheme == 3) { /* fem.hpp:397-404 */
+        double gc[3][5];
+        global_gradient(o, u, c, a, gc);
+        ns_minus_flux_matrix(o, F, &u[(c * n + a) * K], gc);
+      }
       const double *js = &o->jstar[(c * n + a) * 9];
       double *fh = &fhat[(c * n + a) * 15];
       for (int k = 0; k < 5; ++k) for (int d = 0; d < 3; ++d) /* hexahedron.hpp:607-611 */
@@ -636,6 +845,15 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
       if (cs >= 0) {
         int as = o->s_node[f * fq + p];
         flux_upwind(o->riemann, fr, uh, &u[(cs * n + as) * K], fu);
+        if (o->scheme == 3) { /* fr/general.hpp:316-350 */
+          const double *us = &u[(cs * n + as) * K];
+          double gh_[3][5], gs_[3][5], hh[6][5], hs[6][5], gcm[3][5], ucm[5];
+          global_gradient_hessian(o, u, ch, ah, gh_, hh);
+          global_gradient_hessian(o, u, cs, as, gs_, hs);
+          ddg_common_gradient(o, o->dist[f * fq + p], fr->a, uh, us, gh_, gs_, hh, hs, gcm);
+          for (int k = 0; k < 5; ++k) ucm[k] = (uh[k] + us[k]) / 2;
+          ns_minus_flux_normal(o, fu, ucm, gcm, fr->a);
+        }
         if (o->scheme == 2) { /* fr/general.hpp:296-315, 409-434: the whole node line is corrected */
           double sh = o->h_scale[f * fq + p], ss = o->s_scale[f * fq + p];
           const double *Fh = &fhat[(ch * n + ah) * 15], *Fs = &fhat[(cs * n + as) * 15];
@@ -654,7 +872,7 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
               }
             }
           }
-        } else if (o->scheme == 0) { /* fr/general.hpp:296-315, fr/lobatto.hpp:232-251 */
+        } else if (o->scheme == 0 || o->scheme == 3) { /* fr/general.hpp:296-315, fr/lobatto.hpp:232-251 */
           double sh = o->h_scale[f * fq + p], ss = o->s_scale[f * fq + p];
           double gh = sh > 0 ? gp : -gp, gs = ss > 0 ? gp : -gp;
           const double *Fh = &fhat[(ch * n + ah) * 15], *Fs = &fhat[(cs * n + as) * 15];
@@ -675,7 +893,16 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
         int tag = o->tag[f], kind = o->bc_kind[tag];
         double given[5] = {0, 0, 0, 0, 0};
         if (kind >= 2) eval_field(o->field_kind[tag], o->field_prm[tag], &o->fxyz[(f * fq + p) * 3], t, given);
-        boundary_flux(o->riemann, kind, fr, uh, given, fu);
+        if (kind == 6) { /* no-slip wall: fr/lobatto.hpp:301-319, fr/general.hpp:460-479; no term at all for
+                            inviscid systems (fr/general.hpp:455-459) */
+          if (o->scheme != 3) continue;
+          double gh_[3][5];
+          boundary_flux(o->riemann, 0, fr, uh, given, fu);
+          global_gradient(o, u, ch, ah, gh_);
+          ns_minus_flux_no_slip(o, fu, given, uh, gh_, fr->a, o->beta0 / o->dist[f * fq + p]);
+        } else {
+          boundary_flux(o->riemann, kind, fr, uh, given, fu);
+        }
         if (o->scheme == 2) { /* fr/general.hpp:435-640 */
           double sh = o->h_scale[f * fq + p];
           const double *Fh = &fhat[(ch * n + ah) * 15];
@@ -687,7 +914,7 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
             for (int k = 0; k < 5; ++k)
               res[(ch * n + base + i * strd[d]) * K + k] -= (fu[k] * sh - Fh[k * 3 + d]) * gpr;
           }
-        } else if (o->scheme == 0) { /* fr/lobatto.hpp:278-428 */
+        } else if (o->scheme == 0 || o->scheme == 3) { /* fr/lobatto.hpp:278-428 */
           double sh = o->h_scale[f * fq + p], gh = sh > 0 ? gp : -gp;
           const double *Fh = &fhat[(ch * n + ah) * 15];
           for (int k = 0; k < 5; ++k) res[(ch * n + ah) * K + k] -= (fu[k] * sh - Fh[k * 3 + o->h_dir[f]]) * gh;
@@ -754,7 +981,7 @@ double oracle_time_step(void *h, const double *u, double dt_guess, int rk_order)
   }
   double dt = cfl[rk_order][o->degree] * min_dt;
   if (dt_guess < dt) dt = dt_guess;
-  if (o->scheme == 0) { dt *= 2.0; if (dt_guess < dt) dt = dt_guess; }
+  if (o->scheme == 0 || o->scheme == 3) { dt *= 2.0; if (dt_guess < dt) dt = dt_guess; }
   return dt;
 }
 

@@ -56,6 +56,9 @@ using Scalar = double;
 #include "mini/riemann/euler/hllc.hpp"
 #include "mini/riemann/euler/types.hpp"
 #include "mini/riemann/rotated/euler.hpp"
+#include "mini/riemann/concept.hpp"
+#include "mini/riemann/diffusive/direct.hpp"
+#include "mini/riemann/diffusive/navier_stokes.hpp"
 #include "mini/spatial/dg/lobatto.hpp"
 #include "mini/spatial/fr/lobatto.hpp"
 #include "mini/temporal/rk.hpp"
@@ -617,6 +620,7 @@ struct SolverImpl : SolverBase {
       case 3: sp->SetSubsonicInlet(name, func); break;
       case 4: sp->SetSubsonicOutlet(name, func); break;
       case 5: sp->SetSmartBoundary(name, func); break;
+      case 6: sp->SetNoSlipWall(name, func); break;
       default: std::abort();
       }
     }
@@ -683,6 +687,14 @@ using RExact = Rotated<mini::riemann::euler::Exact<Gas, 3>>;
 using RHllc = Rotated<mini::riemann::euler::HartenLaxLeerContact<Gas, 3>>;
 using RAusm = Rotated<mini::riemann::euler::AdvectionUpstreamSplittingMethod<Gas, 3>>;
 
+// Navier-Stokes with the direct-DG common gradient, as demo/laminar/shockless.hpp:43-57 composes it
+using Diffusion = mini::riemann::diffusive::Direct<mini::riemann::diffusive::NavierStokes<Gas>>;
+template <class Unrotated>
+using Viscous = mini::riemann::ConvectionDiffusion<Rotated<Unrotated>, Diffusion>;
+using VExact = Viscous<mini::riemann::euler::Exact<Gas, 3>>;
+using VHllc = Viscous<mini::riemann::euler::HartenLaxLeerContact<Gas, 3>>;
+using VAusm = Viscous<mini::riemann::euler::AdvectionUpstreamSplittingMethod<Gas, 3>>;
+
 // c_next of the next fr::General to be created (fr/general.hpp:218-219); set by ref_pN_set_vincent
 static double g_c_next = 0.0;
 
@@ -706,6 +718,12 @@ static SolverBase *Create(int scheme, int riemann, GlobalMesh &&mesh) {
     case 1: return new SolverImpl<sp::fr::General<Part, RHllc>>(std::move(mesh), g_c_next);
     case 2: return new SolverImpl<sp::fr::General<Part, RAusm>>(std::move(mesh), g_c_next);
     }
+  } else if (scheme == 3) {
+    switch (riemann) {
+    case 0: return new SolverImpl<sp::fr::Lobatto<Part, VExact>>(std::move(mesh));
+    case 1: return new SolverImpl<sp::fr::Lobatto<Part, VHllc>>(std::move(mesh));
+    case 2: return new SolverImpl<sp::fr::Lobatto<Part, VAusm>>(std::move(mesh));
+    }
   }
   return nullptr;
 }
@@ -728,6 +746,12 @@ extern "C" {
 int REF_FN(degree)() { return REF_DEGREE; }
 
 void REF_FN(set_vincent)(double c_next) { oracle::g_c_next = c_next; }
+
+// class-static configuration of the diffusive part (direct.hpp:80-83, navier_stokes.hpp:57-60)
+void REF_FN(set_viscous)(double beta_0, double beta_1, double nu, double prandtl) {
+  oracle::Diffusion::SetBetaValues(beta_0, beta_1);
+  oracle::Diffusion::SetProperty(nu, prandtl);
+}
 
 void *REF_FN(create)(int scheme, int riemann, Int n_nodes, const double *xyz, Int n_cells,
     const Int *cell_nodes, const int *cell_parts, int n_parts, Int n_bfaces,

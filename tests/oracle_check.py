@@ -54,6 +54,9 @@ class Oracle:
         except Exception:
             pass
 
+    def set_viscous(self, beta0, beta1, nu, prandtl):
+        lib().oracle_set_viscous(self.h, C.c_double(beta0), C.c_double(beta1), C.c_double(nu), C.c_double(prandtl))
+
     def set_bc(self, tag, bc_kind, field_kind=F_CONST, params=None):
         p = np.zeros(8)
         if params is not None:

@@ -12,10 +12,10 @@ _libs: dict[int, C.CDLL] = {}
 
 CB = C.CFUNCTYPE(None, C.c_int, C.POINTER(C.c_double), C.c_double, C.POINTER(C.c_double), C.c_void_p)
 
-FR, DG, FR_GENERAL = 0, 1, 2
+FR, DG, FR_GENERAL, FR_VISCOUS = 0, 1, 2, 3
 EXACT, HLLC, AUSM = 0, 1, 2
 # boundary kinds, order of fem.hpp:196-222 as used by ref_harness.cpp
-WALL, SUPERSONIC_OUTLET, SUPERSONIC_INLET, SUBSONIC_INLET, SUBSONIC_OUTLET, SMART = range(6)
+WALL, SUPERSONIC_OUTLET, SUPERSONIC_INLET, SUBSONIC_INLET, SUBSONIC_OUTLET, SMART, NO_SLIP = range(7)
 # field kinds of ref_harness.cpp::EvalField
 F_CONST, F_VORTEX, F_CALLBACK, F_SMOOTH = range(4)
 
@@ -115,6 +115,10 @@ class Ref:
         c = CB(cb) if cb is not None else C.cast(None, CB)
         self._keep.append(c)
         return C.c_int(kind), _dp(p), C.c_int(16), c, None
+
+    def set_viscous(self, beta0, beta1, nu, prandtl):
+        """class statics of the reference (direct.hpp:80-83, navier_stokes.hpp:57-60): process-wide"""
+        self._f("set_viscous")(C.c_double(beta0), C.c_double(beta1), C.c_double(nu), C.c_double(prandtl))
 
     def set_bc(self, tag, bc_kind, field_kind=F_CONST, params=None, cb=None):
         self._f("set_bc")(self.h, C.c_int(tag), C.c_int(bc_kind), *self._field(field_kind, params, cb))
