@@ -48,6 +48,8 @@ def parse():
     ap.add_argument("--riemann", default="hllc", choices=list(RIEMANN))
     ap.add_argument("--scheme", default="fr", choices=["fr", "dg"])
     ap.add_argument("--cpu-cells", type=int, default=0, help="cells per direction of the CPU sample (0 = auto)")
+    ap.add_argument("--viscous", type=float, default=None, metavar="NU",
+                    help="run the Navier-Stokes + direct-DG path with this kinematic viscosity (not the headline workload)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of replaying a CUDA graph")
@@ -130,6 +132,8 @@ def cpu_run(args, steps, warmup, cells=None):
     from minicfd_b200.part import cell_points
     cores = os.cpu_count() or 1
     scheme = 0 if args.scheme == "fr" else 1
+    if args.viscous is not None:
+        scheme = 3
     riemann = RIEMANN[args.riemann]
     kf = 5 * (args.degree + 1) ** 3
     if refapi.available(args.degree):
@@ -142,6 +146,8 @@ def cpu_run(args, steps, warmup, cells=None):
         px, py, pz = meshmod.factor3(n_parts)
         parts = meshmod.block_partition(m, px, py, pz)
         r = refapi.Ref(m, degree=args.degree, scheme=scheme, riemann=riemann, cell_parts=parts, n_parts=n_parts)
+        if args.viscous is not None:
+            r.set_viscous(2.0, 1.0 / 12, args.viscous, 0.708)
         for tag in range(6):
             r.set_bc(tag, refapi.WALL)
         r.approximate(refapi.F_VORTEX, [5.0, 5.0, 1.0, 1.0, 0.0, 5.0])
@@ -153,6 +159,8 @@ def cpu_run(args, steps, warmup, cells=None):
         n = cells or args.cpu_cells or 12
         m = meshmod.box(n, n, n, hi=(10.0, 10.0, 10.0))
         o = oc.Oracle(m, args.degree, scheme, riemann)
+        if args.viscous is not None:
+            o.set_viscous(2.0, 1.0 / 12, args.viscous, 0.708)
         for tag in range(6):
             o.set_bc(tag, 0)
         state = {"u": o.approximate(oc.F_VORTEX, [5.0, 5.0, 1.0, 1.0, 0.0, 5.0])}
@@ -177,7 +185,10 @@ def cpu_run(args, steps, warmup, cells=None):
 
 def config_dict(args, n_gpus, dims, part):
     return {"workload": f"BASELINE config 2: synthetic structured box, {dims[0]}x{dims[1]}x{dims[2]} Hexahedron8 "
-                        f"cells total ({args.cells}^3 per GPU), Euler isentropic vortex, "
+                        f"cells total ({args.cells}^3 per GPU), "
+                        + ("Euler isentropic vortex, " if args.viscous is None else
+                           f"Navier-Stokes (nu={args.viscous}, direct-DG face flux) on the isentropic vortex, ") +
+                        
                         f"{args.scheme.upper()}-Lobatto p={args.degree}, {args.riemann.upper()}, RK3, periodic",
             "cells_per_gpu": args.cells ** 3, "dof_per_gpu": args.cells ** 3 * 5 * (args.degree + 1) ** 3,
             "step": "GetTimeStep + RungeKutta<3>::Update (3 stages)", "parallelism": f"domain decomposition {part}",
@@ -235,7 +246,9 @@ def ours(args):
     scheme = capi.FR_LOBATTO if args.scheme == "fr" else capi.DG_LOBATTO
     comm = halo.for_part(part, 5 * (args.degree + 1) ** 3) if world > 1 else None
     sp = Spatial(part, scheme=scheme, degree=args.degree, riemann=RIEMANN[args.riemann], device=local_rank,
-                 comm=comm)
+                 comm=comm, diffusion=capi.INVISCID if args.viscous is None else capi.NAVIER_STOKES_DDG)
+    if args.viscous is not None:
+        sp.SetDiffusion(2.0, 1.0 / 12, args.viscous, 0.708)
     sp.ctx.set_stream(torch.cuda.current_stream().cuda_stream)
     sp.Approximate(lambda x: fields.vortex()(x, 0.0))
     if comm is not None:

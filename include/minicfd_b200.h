@@ -63,12 +63,20 @@ typedef enum {
   MCFD_BC_NO_SLIP_WALL = 6
 } mcfd_bc_kind;
 
+/* Diffusive part of the Riemann type.  MCFD_NAVIER_STOKES_DDG = mini::riemann::ConvectionDiffusion<
+ * rotated::Euler<..>, diffusive::Direct<diffusive::NavierStokes<Gas>>> as composed in
+ * demo/laminar/shockless.hpp:43-57 (include/mini/riemann/concept.hpp:93-121, diffusive/navier_stokes.hpp,
+ * diffusive/direct.hpp), on expansions with kLocal == false. */
+typedef enum { MCFD_INVISCID = 0, MCFD_NAVIER_STOKES_DDG = 1 } mcfd_diffusion;
+
 typedef struct {
   int32_t scheme;    /* mcfd_scheme */
   int32_t degree;    /* P: 2 or 3 (template parameter kDegrees, demo/euler/sourceless.hpp:27) */
   int32_t riemann;   /* mcfd_riemann */
   int32_t device;    /* CUDA device ordinal, -1 = current device */
   double fr_c_next;  /* MCFD_FR_GENERAL only: the `c_next` of fr::General(part, c_next), fr/general.hpp:218-219 */
+  int32_t diffusion; /* mcfd_diffusion; the viscous path exists for MCFD_FR_LOBATTO */
+  int32_t reserved;  /* 0 */
 } mcfd_config;
 
 /* -- life cycle ------------------------------------------------------------------------------ */
@@ -134,6 +142,20 @@ int mcfd_set_boundary_values(mcfd_ctx *ctx, int32_t tag, const double *values);
  * time-dependent boundary functions can be re-sampled (fem.hpp:225-227 SetTime). */
 typedef void (*mcfd_time_callback)(void *user, double t);
 int mcfd_set_time_callback(mcfd_ctx *ctx, mcfd_time_callback fn, void *user);
+
+/* -- diffusive part (MCFD_NAVIER_STOKES_DDG contexts) -------------------------------------------- */
+
+/* Replaces the class-static setters `Riemann::Diffusion::SetBetaValues(beta_0, beta_1)`
+ * (include/mini/riemann/diffusive/direct.hpp:80-83) and `Riemann::Diffusion::SetProperty(nu, prandtl)`
+ * (include/mini/riemann/diffusive/navier_stokes.hpp:57-60) as demo/laminar/cavity.cpp:50-51 calls them;
+ * per context here.  Defaults: beta = (2, 1/12), nu = 0.  With it the residual becomes the one of
+ * fr::Lobatto on ConvectionDiffusion: viscous volume flux (fem.hpp:397-404, navier_stokes.hpp:150-175),
+ * direct-DG common gradient and viscous face flux (fr/general.hpp:316-350, direct.hpp:45-78,
+ * navier_stokes.hpp:193-202) from the nodal gradients and Hessians of both cells
+ * (polynomial/hexahedron.hpp:479-524, 586-594), with the distance of fem.hpp:83-85; MCFD_BC_NO_SLIP_WALL
+ * becomes fr/general.hpp:460-479 + navier_stokes.hpp:204-224, its boundary values being
+ * (unused, wall velocity u v w, normal temperature gradient) as in demo/laminar/cavity.cpp:30-38. */
+int mcfd_set_diffusion(mcfd_ctx *ctx, double beta_0, double beta_1, double nu, double prandtl);
 
 /* -- temporal::System interface (include/mini/temporal/ode.hpp:17-48) -------------------------- */
 

@@ -12,6 +12,7 @@ LIB_PATH = os.path.join(HERE, "libminicfd_b200.so")
 
 FR_LOBATTO, DG_LOBATTO, FR_GENERAL = 0, 1, 2
 EXACT, HLLC, AUSM = 0, 1, 2
+INVISCID, NAVIER_STOKES_DDG = 0, 1
 (BC_INVISCID_WALL, BC_SUPERSONIC_OUTLET, BC_SUPERSONIC_INLET, BC_SUBSONIC_INLET, BC_SUBSONIC_OUTLET,
  BC_SMART, BC_NO_SLIP_WALL) = range(7)
 
@@ -20,7 +21,7 @@ TIME_CALLBACK = C.CFUNCTYPE(None, C.c_void_p, C.c_double)
 
 class Config(C.Structure):
     _fields_ = [("scheme", C.c_int32), ("degree", C.c_int32), ("riemann", C.c_int32), ("device", C.c_int32),
-                ("fr_c_next", C.c_double)]
+                ("fr_c_next", C.c_double), ("diffusion", C.c_int32), ("reserved", C.c_int32)]
 
 
 class McfdError(RuntimeError):
@@ -51,6 +52,7 @@ SYMBOLS = {
     "mcfd_count_boundary_faces": (C.c_int64, [_P, C.c_int32]),
     "mcfd_get_boundary_points": (C.c_int, [_P, C.c_int32, _D]),
     "mcfd_set_boundary_values": (C.c_int, [_P, C.c_int32, _D]),
+    "mcfd_set_diffusion": (C.c_int, [_P, C.c_double, C.c_double, C.c_double, C.c_double]),
     "mcfd_set_time_callback": (C.c_int, [_P, TIME_CALLBACK, _P]),
     "mcfd_count_local_cells": (C.c_int64, [_P]),
     "mcfd_cell_data_size": (C.c_int64, [_P]),
@@ -118,10 +120,10 @@ def time_step_static(scheme, degree, n_cells, column_ptr, length_ptr, dt_guess, 
 class Context:
     """One mcfd_ctx: a part of the mesh resident on one GPU."""
 
-    def __init__(self, scheme=FR_LOBATTO, degree=2, riemann=HLLC, device=-1, fr_c_next=0.0):
+    def __init__(self, scheme=FR_LOBATTO, degree=2, riemann=HLLC, device=-1, fr_c_next=0.0, diffusion=INVISCID):
         self.lib = load()
         self.h = _P()
-        cfg = Config(scheme, degree, riemann, device, fr_c_next)
+        cfg = Config(scheme, degree, riemann, device, fr_c_next, diffusion, 0)
         rc = self.lib.mcfd_create(C.byref(cfg), C.byref(self.h))
         if rc != 0:
             raise McfdError(f"mcfd_create failed ({rc}): {self.lib.mcfd_last_error(None).decode()}")
@@ -130,6 +132,9 @@ class Context:
         self.kfields = 5 * self.q ** 3
         self.n_local = 0
         self._cb = None
+
+    def set_diffusion(self, beta_0, beta_1, nu, prandtl):
+        self._check(self.lib.mcfd_set_diffusion(self.h, beta_0, beta_1, nu, prandtl))
 
     def _check(self, rc):
         if rc != 0:

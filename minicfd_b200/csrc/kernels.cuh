@@ -48,6 +48,8 @@ struct Tables {
   // - and + end of a node line; the lumped Lobatto scheme only has g[0][0] and g[1][Q-1]
   int general;
   double g[2][kMaxQ];
+  double d1[kMaxQ][kMaxQ];             // l_m'(x_i)  (viscous path: local gradients)
+  double d2[kMaxQ][kMaxQ];             // l_m''(x_i) (viscous path: local Hessians)
   int slot_node[kMaxWarps * kMaxSlots];  // node handled by (warp, slot), -1 = idle
   // face-point index q of node n on its face in direction d (or -1 when not on a face)
   signed char node_q[kMaxN][3];
@@ -71,6 +73,11 @@ struct StageArgs {
   int mode;
   double dt;
   const double *dt_dev;         // when not null the time step is read from device memory instead
+  // viscous path only (ConvectionDiffusion<Euler, Direct<NavierStokes>>): traces written by TraceKernel
+  const double *grad;           // [tile][node*15 + x*5 + c][lane]  global gradient at every node
+  const double *hn;             // [tile][point*15 + x*5 + c][lane] Hessian . own outward unit normal
+  const double *h2s;            // [tile][face*3 + x][lane]         Face::HolderToSharer of my face f
+  Viscosity vis;
 };
 
 enum : int {
@@ -199,6 +206,139 @@ MCFD_HD int FaceOf(int d, bool plus) {  // local face id of the -/+ side in dire
   return (d == 0) ? (plus ? 2 : 4) : (d == 1) ? (plus ? 3 : 1) : (plus ? 5 : 0);
 }
 
+// ---- viscous traces -------------------------------------------------------------------------------
+// What a face point of the direct-DG scheme needs from a cell besides the value (fr/general.hpp:316-350):
+// the gradient and the Hessian of the nodal polynomial in physical space
+// (Hexahedron::GetGlobalValueGradientHessian with kLocal == false, polynomial/hexahedron.hpp:586-594,
+// 496-524).  The Hessian only enters through  (H_sharer - H_holder) . normal  (direct.hpp:66-76), so each
+// cell stores  H . n_own  per face point, n_own its own outward unit normal there; the neighbour's
+// outward normal is the opposite one, hence  jump . n_holder = -(Hn_own + Hn_neighbour)  on both sides.
+//
+//   grad out: rows (n*15 + x*5 + c),  hn out: rows ((f*Q*Q + q)*15 + x*5 + c),  `os` doubles apart.
+//
+// With J = d(x,y,z)/d(xi,eta,zeta) (rows = local directions), inv = J^-1 and T_a = d(J^-T)/d(xi_a) =
+// -(inv dJ_a inv)^T (hexahedron.hpp:233-236), the reference evaluates per component
+//     S(a, j) = sum_b Hl(a, b) inv(j, b) + sum_b gl(b) T_a(b, j),     H = inv S.
+// Contracting with n first:  w = inv^T n,  v_a = w^T dJ_a,  m_a(b) = -sum_s v_a(s) inv(s, b),
+//     t(a) = sum_b Hl(a, b) w(b) + sum_b gl(b) m_a(b),     (H n)(i) = sum_a inv(i, a) t(a).
+// dJ_a of the trilinear map has three distinct rows: A = d2x/dxi deta, B = d2x/dzeta dxi, C = d2x/deta dzeta.
+template <int Q>
+MCFD_HD void TraceCellNode(int n, const double *u, int us, const double *geo, int gs, double *grad,
+    double *hn, int os) {
+  constexpr int FQ = Q * Q;
+  const int idx[3] = {n / FQ, (n / Q) % Q, n % Q};
+  const int str[3] = {FQ, Q, 1};
+  double gl[3][5];
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    const int base = n - idx[d] * str[d];
+#pragma unroll
+    for (int c = 0; c < 5; ++c) gl[d][c] = 0;
+#pragma unroll
+    for (int m = 0; m < Q; ++m) {
+      const double coef = c_tab.d1[idx[d]][m];
+      const double *src = u + (size_t)(base + m * str[d]) * 5 * us;
+#pragma unroll
+      for (int c = 0; c < 5; ++c) gl[d][c] = fma(coef, src[c * us], gl[d][c]);
+    }
+  }
+  const double x = c_tab.xi[idx[0]], e = c_tab.xi[idx[1]], z = c_tab.xi[idx[2]];
+  const Metric m = ComputeMetric(geo, gs, x, e, z);
+  const double inv_det = Rcp(m.det);
+  double inv[3][3];   // inv[xyz][local] = J*(xyz, local) / det
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+#pragma unroll
+    for (int d = 0; d < 3; ++d) inv[k][d] = m.s[d][k] * inv_det;
+  }
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+#pragma unroll
+    for (int c = 0; c < 5; ++c)
+      grad[(size_t)(n * 15 + k * 5 + c) * os] = inv[k][0] * gl[0][c] + inv[k][1] * gl[1][c] + inv[k][2] * gl[2][c];
+  }
+  if (idx[0] != 0 && idx[0] != Q - 1 && idx[1] != 0 && idx[1] != Q - 1 && idx[2] != 0 && idx[2] != Q - 1) return;
+  // local Hessian XX XY XZ YY YZ ZZ (hexahedron.hpp:155-170, 439-447)
+  double hl[6][5];
+#pragma unroll
+  for (int h = 0; h < 6; ++h) {
+#pragma unroll
+    for (int c = 0; c < 5; ++c) hl[h][c] = 0;
+  }
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    const int base = n - idx[d] * str[d];
+    const int h = d == 0 ? 0 : (d == 1 ? 3 : 5);
+#pragma unroll
+    for (int mm = 0; mm < Q; ++mm) {
+      const double coef = c_tab.d2[idx[d]][mm];
+      const double *src = u + (size_t)(base + mm * str[d]) * 5 * us;
+#pragma unroll
+      for (int c = 0; c < 5; ++c) hl[h][c] = fma(coef, src[c * us], hl[h][c]);
+    }
+  }
+#pragma unroll
+  for (int pair = 0; pair < 3; ++pair) {
+    const int d0 = pair == 2 ? 1 : 0, d1 = pair == 0 ? 1 : 2;     // (x,y) (x,z) (y,z)
+    const int h = pair == 0 ? 1 : (pair == 1 ? 2 : 4);
+    const int base = n - idx[d0] * str[d0] - idx[d1] * str[d1];
+#pragma unroll
+    for (int a = 0; a < Q; ++a) {
+      const double ca = c_tab.d1[idx[d0]][a];
+#pragma unroll
+      for (int b = 0; b < Q; ++b) {
+        const double coef = ca * c_tab.d1[idx[d1]][b];
+        const double *src = u + (size_t)(base + a * str[d0] + b * str[d1]) * 5 * us;
+#pragma unroll
+        for (int c = 0; c < 5; ++c) hl[h][c] = fma(coef, src[c * us], hl[h][c]);
+      }
+    }
+  }
+  double A[3], B[3], C[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const double c4 = geo[(9 + k) * gs], c5 = geo[(12 + k) * gs], c6 = geo[(15 + k) * gs], c7 = geo[(18 + k) * gs];
+    A[k] = fma(z, c7, c4);
+    B[k] = fma(e, c7, c6);
+    C[k] = fma(x, c7, c5);
+  }
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    if (idx[d] != 0 && idx[d] != Q - 1) continue;
+    const bool plus = idx[d] != 0;
+    const int pt = FaceOf(d, plus) * FQ + c_tab.node_q[n][d];
+    const double n2 = m.s[d][0] * m.s[d][0] + m.s[d][1] * m.s[d][1] + m.s[d][2] * m.s[d][2];
+    const double sc = (plus ? 1.0 : -1.0) * Rsqrt(n2);
+    const double nrm[3] = {sc * m.s[d][0], sc * m.s[d][1], sc * m.s[d][2]};
+    double w[3], v[3][3], mm[3][3];
+#pragma unroll
+    for (int b = 0; b < 3; ++b) w[b] = nrm[0] * inv[0][b] + nrm[1] * inv[1][b] + nrm[2] * inv[2][b];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      v[0][k] = w[1] * A[k] + w[2] * B[k];
+      v[1][k] = w[0] * A[k] + w[2] * C[k];
+      v[2][k] = w[0] * B[k] + w[1] * C[k];
+    }
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+#pragma unroll
+      for (int b = 0; b < 3; ++b) mm[a][b] = -(v[a][0] * inv[0][b] + v[a][1] * inv[1][b] + v[a][2] * inv[2][b]);
+    }
+#pragma unroll
+    for (int c = 0; c < 5; ++c) {
+      double t[3];
+      t[0] = hl[0][c] * w[0] + hl[1][c] * w[1] + hl[2][c] * w[2];
+      t[1] = hl[1][c] * w[0] + hl[3][c] * w[1] + hl[4][c] * w[2];
+      t[2] = hl[2][c] * w[0] + hl[4][c] * w[1] + hl[5][c] * w[2];
+#pragma unroll
+      for (int a = 0; a < 3; ++a) t[a] += gl[0][c] * mm[a][0] + gl[1][c] * mm[a][1] + gl[2][c] * mm[a][2];
+#pragma unroll
+      for (int k = 0; k < 3; ++k)
+        hn[(size_t)(pt * 15 + k * 5 + c) * os] = inv[k][0] * t[0] + inv[k][1] * t[1] + inv[k][2] * t[2];
+    }
+  }
+}
+
 template <int Q, int CPB, int NW>
 struct SlotStates {
   double u[StageGeometry<Q, CPB, NW>::SLOTS][5];
@@ -240,7 +380,7 @@ MCFD_HD void StagePrologue(const StageArgs &p, int tid, int bid, double *smem) {
 
 // ---- phase A: contravariant fluxes Fhat = F(u) J* at every node -> shared memory --------------
 // (fr/general.hpp:276-279; fem.hpp:392-395; types.hpp:322-333; polynomial/hexahedron.hpp:607-611)
-template <int Q, int CPB, int NW>
+template <int Q, int CPB, int NW, bool kViscous = false>
 MCFD_HD void StagePhaseA(const StageArgs &p, int tid, int bid, double *smem,
     const SlotStates<Q, CPB, NW> &st, SlotResiduals<Q, CPB, NW> *res) {
   using G = StageGeometry<Q, CPB, NW>;
@@ -269,6 +409,16 @@ MCFD_HD void StagePhaseA(const StageArgs &p, int tid, int bid, double *smem,
       fx[x][3] = u[3] * vel[x];
       fx[x][1 + x] += q.p;
       fx[x][4] = h0 * vel[x];
+    }
+    if (kViscous) {   // fem.hpp:397-404: F -= viscous flux of (u, grad u) at the node
+      double gr[3][5];
+      const double *src = p.grad + ((size_t)g.tile * G::N * 15 + n * 15) * kTile + g.tl;
+#pragma unroll
+      for (int x = 0; x < 3; ++x) {
+#pragma unroll
+        for (int c = 0; c < 5; ++c) gr[x][c] = src[(x * 5 + c) * kTile];
+      }
+      NsMinusFluxMatrix(p.vis, u, gr, fx);
     }
     double *dst = g.sF + (size_t)n * 15 * CPB + g.lc;
 #pragma unroll
@@ -370,7 +520,7 @@ MCFD_HD void LoadPoint(const StageArgs &p, const StageGeometry<Q, CPB, NW> &g, i
   }
 }
 
-template <int Q, int kRiemann, int CPB, int NW, bool kGeneral>
+template <int Q, int kRiemann, int CPB, int NW, bool kGeneral, bool kViscous = false>
 MCFD_HD void StagePhaseB2(const StageArgs &p, int tid, int bid, double *smem) {
   using G = StageGeometry<Q, CPB, NW>;
   G g(p, tid, bid, smem);
@@ -408,12 +558,60 @@ MCFD_HD void StagePhaseB2(const StageArgs &p, int tid, int bid, double *smem) {
           ur[c] = holder ? cur.v[c] : cur.u[c];
         }
         FluxUpwind<kRiemann>(ul, ur, hs * nx, hs * ny, hs * nz, fl);
+        if (kViscous) {
+          // direct-DG common gradient (direct.hpp:45-78) and the viscous flux of the averaged state
+          // along the holder's normal (fr/general.hpp:328-337).  In terms of MY outward unit normal o
+          // and (v - u) = neighbour minus own value the expression is the same on both sides:
+          //   G = (g_own + g_nbr)/2 + beta0/dist * o (v - u)^T - beta1*dist * (Hn_own + Hn_nbr)
+          const double os_ = sgn * inv_area;
+          const double o[3] = {os_ * nx, os_ * ny, os_ * nz};
+          const double *hv = p.h2s + ((size_t)g.tile * 18 + f * 3) * kTile + g.tl;
+          const double dh = (hs * nx) * hv[0] + (hs * ny) * hv[kTile] + (hs * nz) * hv[2 * kTile];
+          const double pen0 = p.vis.beta0 * Rcp(dh), pen1 = p.vis.beta1 * dh;
+          const int code = cur.code;
+          const int f2 = code & 7;
+          const int node2 = g.sNbrNode[(f2 * 8 + ((code >> 3) & 7)) * FQ + q];
+          const int d2 = (f2 == 2 || f2 == 4) ? 0 : ((f2 == 1 || f2 == 3) ? 1 : 2);
+          const int pt2 = f2 * FQ + c_tab.node_q[node2][d2];
+          const double *go = p.grad + ((size_t)g.tile * G::N * 15 + n * 15) * kTile + g.tl;
+          const double *ho = p.hn + ((size_t)g.tile * G::POINTS * 15 + pt * 15) * kTile + g.tl;
+          const double *gn = p.grad + ((size_t)(cur.nb >> 5) * G::N * 15 + node2 * 15) * kTile + (cur.nb & 31);
+          const double *hb = p.hn + ((size_t)(cur.nb >> 5) * G::POINTS * 15 + pt2 * 15) * kTile + (cur.nb & 31);
+          double gc[3][5], uc[5];
+#pragma unroll
+          for (int c = 0; c < 5; ++c) uc[c] = (ul[c] + ur[c]) * 0.5;
+#pragma unroll
+          for (int x = 0; x < 3; ++x) {
+#pragma unroll
+            for (int c = 0; c < 5; ++c) {
+              const int r = (x * 5 + c) * kTile;
+              gc[x][c] = (go[r] + gn[r]) * 0.5 + (pen0 * o[x]) * (cur.v[c] - cur.u[c]) - pen1 * (ho[r] + hb[r]);
+            }
+          }
+          NsMinusFluxNormal(p.vis, uc, gc, hs * nx, hs * ny, hs * nz, fl);
+        }
         if (!holder) scale = -scale;
       } else {
         const int b = -1 - cur.nb;
         const int kind = p.bkind[b];
         const double inv = sgn * inv_area;
-        if (kind == kBcNoSlip) {
+        if (kViscous && kind == kBcNoSlip) {
+          // fr/lobatto.hpp:301-319, fr/general.hpp:460-479: inviscid-wall flux minus the viscous flux
+          // with the velocity penalty beta0/dist; `given` = (-, wall velocity, n . grad T)
+          const double *gv = p.bvals + ((size_t)b * FQ + q) * 5;
+          const double wall[5] = {gv[0], gv[1], gv[2], gv[3], gv[4]};
+          BoundaryFlux<kRiemann>(kBcWall, cur.u, wall, inv * nx, inv * ny, inv * nz, fl);
+          const double *hv = p.h2s + ((size_t)g.tile * 18 + f * 3) * kTile + g.tl;
+          const double dh = (inv * nx) * hv[0] + (inv * ny) * hv[kTile] + (inv * nz) * hv[2 * kTile];
+          const double *go = p.grad + ((size_t)g.tile * G::N * 15 + n * 15) * kTile + g.tl;
+          double gr[3][5];
+#pragma unroll
+          for (int x = 0; x < 3; ++x) {
+#pragma unroll
+            for (int c = 0; c < 5; ++c) gr[x][c] = go[(x * 5 + c) * kTile];
+          }
+          NsMinusFluxNoSlip(p.vis, wall, cur.u, gr, inv * nx, inv * ny, inv * nz, p.vis.beta0 * Rcp(dh), fl);
+        } else if (kind == kBcNoSlip) {
           // no face term at all for inviscid systems (fem.hpp:382-383): cancel the node's own
           // face-flux term that phase B1 has already added, -coef_F * sgn * (F(u) . J*col_d) / det
           double fm[5][3];
@@ -508,8 +706,8 @@ MCFD_HD void StagePhaseC(const StageArgs &p, int tid, int bid, double *smem,
 // One CTA-sized block, all phases; `sync` is __syncthreads() on the device and a no-op marker on the
 // host, where RunStageBlockOnHost() below replays the phases thread by thread.
 #ifdef __CUDACC__
-template <int Q, int kRiemann, int CPB, int NW, bool kGeneral>
-__global__ void __launch_bounds__(NW * 32, (Q == 3 ? MCFD_P2_MINB : 1))
+template <int Q, int kRiemann, int CPB, int NW, bool kGeneral, bool kViscous = false>
+__global__ void __launch_bounds__(NW * 32, (Q == 3 && !kViscous ? MCFD_P2_MINB : 1))
 StageKernel(StageArgs p) {
   extern __shared__ double smem[];
   const int tid = threadIdx.x, bid = blockIdx.x;
@@ -518,12 +716,12 @@ StageKernel(StageArgs p) {
   StageLoadSlots<Q, CPB, NW>(p, tid, bid, smem, p.u_in, &su);
   StagePrologue<Q, CPB, NW>(p, tid, bid, smem);
   __syncthreads();
-  StagePhaseA<Q, CPB, NW>(p, tid, bid, smem, su, &res);
+  StagePhaseA<Q, CPB, NW, kViscous>(p, tid, bid, smem, su, &res);
   __syncthreads();
   StagePhaseB1<Q, CPB, NW, kGeneral>(p, tid, bid, smem, &res);
   __syncthreads();
   StageStoreResiduals<Q, CPB, NW>(p, tid, bid, smem, res);
-  StagePhaseB2<Q, kRiemann, CPB, NW, kGeneral>(p, tid, bid, smem);
+  StagePhaseB2<Q, kRiemann, CPB, NW, kGeneral, kViscous>(p, tid, bid, smem);
   // the states needed by the update are requested before the last barrier
   SlotStates<Q, CPB, NW> su0;
   StageLoadSlots<Q, CPB, NW>(p, tid, bid, smem, p.u_in, &su);
@@ -532,7 +730,7 @@ StageKernel(StageArgs p) {
   StagePhaseC<Q, CPB, NW, kGeneral>(p, tid, bid, smem, su, su0, res);
 }
 #else
-template <int Q, int kRiemann, int CPB, int NW, bool kGeneral>
+template <int Q, int kRiemann, int CPB, int NW, bool kGeneral, bool kViscous = false>
 void RunStageBlockOnHost(const StageArgs &p, int bid, double *smem) {
   constexpr int T = NW * 32;
   static SlotStates<Q, CPB, NW> su[T], su0[T];
@@ -541,14 +739,53 @@ void RunStageBlockOnHost(const StageArgs &p, int bid, double *smem) {
     StageLoadSlots<Q, CPB, NW>(p, t, bid, smem, p.u_in, &su[t]);
     StagePrologue<Q, CPB, NW>(p, t, bid, smem);
   }
-  for (int t = 0; t < T; ++t) StagePhaseA<Q, CPB, NW>(p, t, bid, smem, su[t], &res[t]);
+  for (int t = 0; t < T; ++t) StagePhaseA<Q, CPB, NW, kViscous>(p, t, bid, smem, su[t], &res[t]);
   for (int t = 0; t < T; ++t) StagePhaseB1<Q, CPB, NW, kGeneral>(p, t, bid, smem, &res[t]);
   for (int t = 0; t < T; ++t) StageStoreResiduals<Q, CPB, NW>(p, t, bid, smem, res[t]);
   for (int t = 0; t < T; ++t) {
-    StagePhaseB2<Q, kRiemann, CPB, NW, kGeneral>(p, t, bid, smem);
+    StagePhaseB2<Q, kRiemann, CPB, NW, kGeneral, kViscous>(p, t, bid, smem);
     StageLoadSlots<Q, CPB, NW>(p, t, bid, smem, p.mode >= kModeRk3b ? p.u0 : p.u_in, &su0[t]);
   }
   for (int t = 0; t < T; ++t) StagePhaseC<Q, CPB, NW, kGeneral>(p, t, bid, smem, su[t], su0[t], res[t]);
+}
+#endif
+
+// Traces of cells [cell_begin, cell_end) (local and ghost alike): one CTA per tile, the tile's state and
+// geometry staged in shared memory, lanes = cells, nodes dealt to the warps.
+template <int Q>
+struct TraceShape {
+  static constexpr int N = Q * Q * Q, F = 5 * N, NW = 8;
+  static constexpr size_t kSharedBytes = (size_t)(F + kGeomRows) * kTile * sizeof(double);
+};
+#ifdef __CUDACC__
+template <int Q>
+__global__ void __launch_bounds__(256, 1) TraceKernel(const double *u, const double *geom, double *grad,
+    double *hn, int tile_begin, int cell_begin, int cell_end) {
+  using S = TraceShape<Q>;
+  extern __shared__ double smem[];
+  double *sU = smem, *sG = smem + S::F * kTile;
+  const int tile = tile_begin + blockIdx.x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const double *src = u + (size_t)tile * S::F * kTile;
+  for (int i = threadIdx.x; i < S::F * kTile; i += S::NW * 32) sU[i] = src[i];
+  for (int i = threadIdx.x; i < kGeomRows * kTile; i += S::NW * 32) sG[i] = geom[(size_t)tile * kGeomRows * kTile + i];
+  __syncthreads();
+  const int cell = tile * kTile + lane;
+  if (cell < cell_begin || cell >= cell_end) return;
+  double *gdst = grad + (size_t)tile * S::N * 15 * kTile + lane;
+  double *hdst = hn + (size_t)tile * 6 * Q * Q * 15 * kTile + lane;
+  for (int n = warp; n < S::N; n += S::NW) TraceCellNode<Q>(n, sU + lane, kTile, sG + lane, kTile, gdst, hdst, kTile);
+}
+#else
+template <int Q>
+void RunTraceOnHost(const double *u, const double *geom, double *grad, double *hn, int n_cells) {
+  constexpr int N = Q * Q * Q, F = 5 * N;
+  for (int cell = 0; cell < n_cells; ++cell) {
+    const int tile = cell >> 5, lane = cell & 31;
+    for (int n = 0; n < N; ++n)
+      TraceCellNode<Q>(n, u + (size_t)tile * F * kTile + lane, kTile, geom + (size_t)tile * kGeomRows * kTile + lane,
+          kTile, grad + (size_t)tile * N * 15 * kTile + lane, hn + (size_t)tile * 6 * Q * Q * 15 * kTile + lane, kTile);
+  }
 }
 #endif
 

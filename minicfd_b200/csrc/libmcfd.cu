@@ -51,6 +51,9 @@ struct mcfd_ctx {
   std::vector<unsigned char> bkind_host;
   std::map<int32_t, int32_t> tag_kind;
   DevBuf<double> u[3], res, geom, bvals, length, column;
+  DevBuf<double> grad, hn, h2s;                 // viscous traces (TraceKernel) and HolderToSharer vectors
+  Viscosity vis{2.0, 1.0 / 12, 0.0, 0.0};       // Direct::SetBetaValues / NavierStokes::SetProperty
+  double prandtl = 0.708;
   DevBuf<int> nbr, send_cells, recv_cells;
   DevBuf<unsigned char> code, bkind;
   DevBuf<double> send_buf, recv_buf;
@@ -86,10 +89,10 @@ int Fail(mcfd_ctx *ctx, int status, std::string msg) {
       return Fail(ctx, MCFD_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
   } while (0)
 
-template <int Q, int R, int CPB, int NW, bool kGeneral>
+template <int Q, int R, int CPB, int NW, bool kGeneral, bool kViscous = false>
 cudaError_t LaunchStageG(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
   size_t smem = StageGeometry<Q, CPB, NW>::kSharedBytes;
-  auto kernel = StageKernel<Q, R, CPB, NW, kGeneral>;
+  auto kernel = StageKernel<Q, R, CPB, NW, kGeneral, kViscous>;
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -103,6 +106,7 @@ cudaError_t LaunchStageG(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
 // the general Vincent correction (fr::General) is a separate instantiation: the lumped schemes pay nothing
 template <int Q, int R, int CPB, int NW>
 cudaError_t LaunchStageT(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
+  if (ctx->cfg.diffusion == MCFD_NAVIER_STOKES_DDG) return LaunchStageG<Q, R, CPB, NW, false, true>(ctx, a, n_blocks);
   return ctx->cfg.scheme == MCFD_FR_GENERAL ? LaunchStageG<Q, R, CPB, NW, true>(ctx, a, n_blocks)
                                             : LaunchStageG<Q, R, CPB, NW, false>(ctx, a, n_blocks);
 }
@@ -116,6 +120,33 @@ cudaError_t LaunchStageQ(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
   }
 }
 
+// Viscous traces (gradient at the nodes, Hessian . normal at the face points) of cells
+// [cell_begin, cell_end) of the state `u`.
+int LaunchTrace(mcfd_ctx *ctx, const double *u, int64_t cell_begin, int64_t cell_end) {
+  if (cell_end <= cell_begin) return MCFD_OK;
+  const int tile_begin = (int)(cell_begin / kTile), tile_end = (int)((cell_end + kTile - 1) / kTile);
+  cudaError_t e;
+  if (ctx->q == 3) {
+    TraceKernel<3><<<tile_end - tile_begin, 256, TraceShape<3>::kSharedBytes, ctx->stream>>>(u, ctx->geom.p,
+        ctx->grad.p, ctx->hn.p, tile_begin, (int)cell_begin, (int)cell_end);
+    e = cudaGetLastError();
+  } else {
+    auto kernel = TraceKernel<4>;
+    static bool configured = false;
+    if (!configured) {
+      e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TraceShape<4>::kSharedBytes);
+      if (e != cudaSuccess) return Fail(ctx, MCFD_ERR_CUDA, cudaGetErrorString(e));
+      configured = true;
+    }
+    kernel<<<tile_end - tile_begin, 256, TraceShape<4>::kSharedBytes, ctx->stream>>>(u, ctx->geom.p, ctx->grad.p,
+        ctx->hn.p, tile_begin, (int)cell_begin, (int)cell_end);
+    e = cudaGetLastError();
+  }
+  if (e != cudaSuccess) return Fail(ctx, MCFD_ERR_CUDA, std::string("trace kernel: ") + cudaGetErrorString(e));
+  ctx->launches++;
+  return MCFD_OK;
+}
+
 // Launch the stage kernel over CTA blocks [block_begin, block_end).
 int LaunchStage(mcfd_ctx *ctx, const double *u_in, const double *u0, double *u_out, int mode,
     double dt, int64_t block_begin, int64_t block_end) {
@@ -127,6 +158,7 @@ int LaunchStage(mcfd_ctx *ctx, const double *u_in, const double *u0, double *u_o
   a.n_local = (int)ctx->mesh.n_local;
   a.block_begin = (int)block_begin;
   a.mode = mode; a.dt = dt; a.dt_dev = ctx->rk_order ? ctx->rk_dt_dev : nullptr;
+  a.grad = ctx->grad.p; a.hn = ctx->hn.p; a.h2s = ctx->h2s.p; a.vis = ctx->vis;
   int n_blocks = (int)(block_end - block_begin);
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (ctx->timing) {
@@ -225,6 +257,10 @@ int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
     return Fail(nullptr, MCFD_ERR_ARG, "unknown scheme");
   if (config->riemann < MCFD_EXACT || config->riemann > MCFD_AUSM)
     return Fail(nullptr, MCFD_ERR_ARG, "unknown Riemann solver");
+  if (config->diffusion != MCFD_INVISCID && config->diffusion != MCFD_NAVIER_STOKES_DDG)
+    return Fail(nullptr, MCFD_ERR_ARG, "unknown diffusion model");
+  if (config->diffusion != MCFD_INVISCID && config->scheme != MCFD_FR_LOBATTO)
+    return Fail(nullptr, MCFD_ERR_ARG, "the viscous path is built for MCFD_FR_LOBATTO only");
   int n_dev = 0;
   cudaError_t e = cudaGetDeviceCount(&n_dev);
   if (e != cudaSuccess || n_dev == 0)
@@ -299,6 +335,15 @@ int mcfd_set_mesh(mcfd_ctx *ctx, int64_t n_nodes, const double *xyz, int64_t n_l
     MCFD_CUDA(ctx, cudaMemset(b.p, 0, state * sizeof(double)));
   }
   ctx->res.Free();
+  if (ctx->cfg.diffusion != MCFD_INVISCID) {
+    auto h2s = ToTiles(ctx->mesh.h2s, 18, ctx->n_cells, ctx->n_tiles);
+    MCFD_CUDA(ctx, ctx->h2s.Alloc(h2s.size()));
+    MCFD_CUDA(ctx, cudaMemcpy(ctx->h2s.p, h2s.data(), h2s.size() * sizeof(double), cudaMemcpyHostToDevice));
+    MCFD_CUDA(ctx, ctx->grad.Alloc((size_t)ctx->n_tiles * ctx->n_nodes * 15 * kTile));
+    MCFD_CUDA(ctx, ctx->hn.Alloc((size_t)ctx->n_tiles * 6 * ctx->q * ctx->q * 15 * kTile));
+    MCFD_CUDA(ctx, cudaMemset(ctx->grad.p, 0, ctx->grad.n * sizeof(double)));
+    MCFD_CUDA(ctx, cudaMemset(ctx->hn.p, 0, ctx->hn.n * sizeof(double)));
+  }
   size_t nb = ctx->mesh.bound_faces.size();
   ctx->btag_of_face.resize(nb);
   for (size_t b = 0; b < nb; ++b) ctx->btag_of_face[b] = ctx->mesh.bound_faces[b].tag;
@@ -444,6 +489,18 @@ int mcfd_set_boundary_values(mcfd_ctx *ctx, int32_t tag, const double *values) {
   return MCFD_OK;
 }
 
+int mcfd_set_diffusion(mcfd_ctx *ctx, double beta_0, double beta_1, double nu, double prandtl) {
+  if (!ctx) return MCFD_ERR_ARG;
+  if (ctx->cfg.diffusion == MCFD_INVISCID) return Fail(ctx, MCFD_ERR_STATE, "the context was created inviscid");
+  if (!(prandtl > 0) || nu < 0) return Fail(ctx, MCFD_ERR_ARG, "need nu >= 0 and prandtl > 0");
+  ctx->vis.beta0 = beta_0;
+  ctx->vis.beta1 = beta_1;
+  ctx->vis.nu = nu;
+  ctx->vis.cond = nu * (kGasR * kGammaOverGm1) / prandtl;   // nu * Cp / Pr (navier_stokes.hpp:76-79)
+  ctx->prandtl = prandtl;
+  return MCFD_OK;
+}
+
 int mcfd_set_time_callback(mcfd_ctx *ctx, mcfd_time_callback fn, void *user) {
   if (!ctx) return MCFD_ERR_ARG;
   ctx->time_cb = fn;
@@ -500,6 +557,9 @@ int mcfd_residual(mcfd_ctx *ctx, double t, double *column, double *column_dev) {
   if (ctx->res.n < state) MCFD_CUDA(ctx, ctx->res.Alloc(state));
   if (ctx->time_cb) ctx->time_cb(ctx->time_user, t);
   const double *u = ctx->u[ctx->cur].p;
+  if (ctx->cfg.diffusion != MCFD_INVISCID) {
+    if (int s = LaunchTrace(ctx, u, 0, ctx->n_cells)) return s;
+  }
   if (int s = LaunchStage(ctx, u, u, ctx->res.p, kModeResidual, 0.0, 0, ctx->total_blocks)) return s;
   if (column_dev) {
     if (int s = LaunchConvert<false>(ctx, ctx->res.p, column_dev, nullptr, ctx->mesh.n_local)) return s;
@@ -549,6 +609,9 @@ int mcfd_rk_stage_inner(mcfd_ctx *ctx, int stage) {
   StageBuffers(ctx, stage, &in, &out, &mode);
   if (in != ctx->rk_in) return Fail(ctx, MCFD_ERR_STATE, "stages must be run in order");
   if (ctx->time_cb) ctx->time_cb(ctx->time_user, mcfd_rk_stage_time(ctx, stage));
+  if (ctx->cfg.diffusion != MCFD_INVISCID) {   // the inner cells' neighbours are all local
+    if (int s = LaunchTrace(ctx, ctx->u[in].p, 0, ctx->mesh.n_local)) return s;
+  }
   return LaunchStage(ctx, ctx->u[in].p, ctx->u[ctx->rk_u0].p, ctx->u[out].p, mode, ctx->rk_dt, 0,
       ctx->inner_blocks);
 }
@@ -560,6 +623,9 @@ int mcfd_rk_stage_inter(mcfd_ctx *ctx, int stage) {
   int in, out, mode;
   StageBuffers(ctx, stage, &in, &out, &mode);
   if (in != ctx->rk_in) return Fail(ctx, MCFD_ERR_STATE, "stages must be run in order");
+  if (ctx->cfg.diffusion != MCFD_INVISCID) {   // the ghost cells hold this stage's values by now
+    if (int s = LaunchTrace(ctx, ctx->u[in].p, ctx->mesh.n_local, ctx->n_cells)) return s;
+  }
   if (int s = LaunchStage(ctx, ctx->u[in].p, ctx->u[ctx->rk_u0].p, ctx->u[out].p, mode, ctx->rk_dt,
           ctx->inner_blocks, ctx->total_blocks)) return s;
   ctx->rk_in = out;

@@ -468,5 +468,101 @@ MCFD_NOINLINE State5 BoundaryFluxOutOfLine(int kind, State5 ui, State5 given, do
   return f;
 }
 
+// ---- diffusive part: NavierStokes<Gas> (riemann/diffusive/navier_stokes.hpp) ----------------------
+// Gradients are g[direction x,y,z][component].  `cond` = nu * Cp / Pr, so that kappa = cond * rho
+// (navier_stokes.hpp:70-79; Cp = R gamma / (gamma - 1), types.hpp:245).
+struct Viscosity {
+  double beta0, beta1;   // Direct::SetBetaValues (direct.hpp:80-83)
+  double nu, cond;       // NavierStokes::SetProperty (navier_stokes.hpp:57-60)
+};
+
+// NavierStokes::ConservativeToPrimitive with gradients (navier_stokes.hpp:91-125): velocity
+// gradient gv[direction][velocity component] and temperature gradient gt[direction].
+MCFD_HD Prim NsPrimitiveGradient(const double *u, const double (*g)[5], double (*gv)[3], double *gt) {
+  Prim q = ConsToPrim(u[0], u[1], u[2], u[3], u[4]);
+  const double inv_rho = Rcp(q.rho);
+#pragma unroll
+  for (int x = 0; x < 3; ++x) {
+    gv[x][0] = (g[x][1] - q.u * g[x][0]) * inv_rho;
+    gv[x][1] = (g[x][2] - q.v * g[x][0]) * inv_rho;
+    gv[x][2] = (g[x][3] - q.w * g[x][0]) * inv_rho;
+    double gp = q.u * g[x][1] + u[1] * gv[x][0];
+    gp += q.v * g[x][2] + u[2] * gv[x][1];
+    gp += q.w * g[x][3] + u[3] * gv[x][2];
+    gp = (g[x][4] - 0.5 * gp) * kGm1;
+    gt[x] = (gp * inv_rho - (q.p * inv_rho * inv_rho) * g[x][0]) * (1.0 / kGasR);
+  }
+  return q;
+}
+
+// GetViscousStressTensor with Stokes' hypothesis (navier_stokes.hpp:127-142); tau = XX XY XZ YY YZ ZZ
+MCFD_HD void NsStress(const double (*gv)[3], double mu, double *tau) {
+  const double div = gv[0][0] + gv[1][1] + gv[2][2];
+  const double zeta = (-2.0 / 3) * mu;
+  tau[0] = 2 * mu * gv[0][0] + zeta * div;
+  tau[3] = 2 * mu * gv[1][1] + zeta * div;
+  tau[5] = 2 * mu * gv[2][2] + zeta * div;
+  tau[1] = mu * (gv[1][0] + gv[0][1]);
+  tau[4] = mu * (gv[2][1] + gv[1][2]);
+  tau[2] = mu * (gv[0][2] + gv[2][0]);
+}
+
+MCFD_HD double SymTau(const double *tau, int x, int y) {
+  return tau[x == y ? (x == 0 ? 0 : (x == 1 ? 3 : 5)) : (x + y == 1 ? 1 : (x + y == 2 ? 2 : 4))];
+}
+
+// MinusViscousFlux on a flux matrix fx[direction][component] (navier_stokes.hpp:150-175)
+MCFD_HD void NsMinusFluxMatrix(const Viscosity &vis, const double *u, const double (*g)[5], double (*fx)[5]) {
+  double gv[3][3], gt[3], tau[6];
+  const Prim q = NsPrimitiveGradient(u, g, gv, gt);
+  NsStress(gv, vis.nu * u[0], tau);
+  const double kappa = vis.cond * u[0];
+#pragma unroll
+  for (int x = 0; x < 3; ++x) {
+    const double t0 = SymTau(tau, x, 0), t1 = SymTau(tau, x, 1), t2 = SymTau(tau, x, 2);
+    fx[x][1] -= t0; fx[x][2] -= t1; fx[x][3] -= t2;
+    fx[x][4] -= kappa * gt[x] + (t0 * q.u + t1 * q.v + t2 * q.w);
+  }
+}
+
+// _MinusViscousFlux (navier_stokes.hpp:178-190): normal flux with given velocity and n . grad T
+MCFD_HD void NsMinusFluxCore(const Viscosity &vis, double rho, const double (*gv)[3], double nx, double ny,
+    double nz, double vu, double vv, double vw, double n_dot_grad_t, double *flux) {
+  double tau[6];
+  NsStress(gv, vis.nu * rho, tau);
+  double work[3];
+#pragma unroll
+  for (int x = 0; x < 3; ++x) {
+    const double t0 = SymTau(tau, x, 0), t1 = SymTau(tau, x, 1), t2 = SymTau(tau, x, 2);
+    flux[1 + x] -= t0 * nx + t1 * ny + t2 * nz;
+    work[x] = t0 * vu + t1 * vv + t2 * vw;
+  }
+  flux[4] -= (work[0] * nx + work[1] * ny + work[2] * nz) + (vis.cond * rho) * n_dot_grad_t;
+}
+
+// MinusViscousFlux along a normal (navier_stokes.hpp:193-202)
+MCFD_HD void NsMinusFluxNormal(const Viscosity &vis, const double *u, const double (*g)[5], double nx,
+    double ny, double nz, double *flux) {
+  double gv[3][3], gt[3];
+  const Prim q = NsPrimitiveGradient(u, g, gv, gt);
+  NsMinusFluxCore(vis, u[0], gv, nx, ny, nz, q.u, q.v, q.w, nx * gt[0] + ny * gt[1] + nz * gt[2], flux);
+}
+
+// MinusViscousFluxOnNoSlipWall (navier_stokes.hpp:204-224): `wall` = (unused, u, v, w, n . grad T)
+MCFD_HD void NsMinusFluxNoSlip(const Viscosity &vis, const double *wall, const double *u, const double (*g)[5],
+    double nx, double ny, double nz, double value_penalty, double *flux) {
+  double gv[3][3], gt[3];
+  const Prim q = NsPrimitiveGradient(u, g, gv, gt);
+  const double pen[3] = {value_penalty * (wall[1] - q.u), value_penalty * (wall[2] - q.v),
+                         value_penalty * (wall[3] - q.w)};
+  const double n[3] = {nx, ny, nz};
+#pragma unroll
+  for (int x = 0; x < 3; ++x) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) gv[x][k] += n[x] * pen[k];
+  }
+  NsMinusFluxCore(vis, u[0], gv, nx, ny, nz, wall[1], wall[2], wall[3], wall[4], flux);
+}
+
 }  // namespace mcfd
 #endif  // MINICFD_B200_PHYSICS_CUH_

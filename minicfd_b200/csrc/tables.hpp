@@ -56,6 +56,24 @@ inline double LagrangeDerivative(int q, const double *x, int m, int i) {
 }
 
 // Vincent::LocalToRightDerivative(1) with c = HuynhLumpingLobatto (basis/vincent.hpp:31-33, 75-91).
+// l_m''(x_i) (basis/lagrange.hpp:130-133 with k = 2)
+inline double LagrangeSecondDerivative(int q, const double *x, int m, int i) {
+  double sum = 0;
+  for (int k = 0; k < q; ++k) {
+    if (k == m) continue;
+    for (int j = 0; j < q; ++j) {
+      if (j == m || j == k) continue;
+      double prod = 1.0 / ((x[m] - x[k]) * (x[m] - x[j]));
+      for (int l = 0; l < q; ++l) {
+        if (l == m || l == k || l == j) continue;
+        prod *= (x[i] - x[l]) / (x[m] - x[l]);
+      }
+      sum += prod;
+    }
+  }
+  return sum;
+}
+
 inline double HuynhLumpedGPrimeAtOne(int degree) {
   double c_next = degree / (2.0 * degree + 1), c_prev = 1 - c_next;
   double prev = 0, curr = 0, next = 0;
@@ -112,6 +130,11 @@ inline Tables BuildTables(int degree, int scheme, int n_warps, int sub, double c
   double x[kMaxQ], w[kMaxQ];
   LobattoRule(q, x, w);
   for (int i = 0; i < q; ++i) { t.xi[i] = x[i]; t.w[i] = w[i]; }
+  for (int i = 0; i < q; ++i)
+    for (int m = 0; m < q; ++m) {
+      t.d1[i][m] = LagrangeDerivative(q, x, m, i);
+      t.d2[i][m] = LagrangeSecondDerivative(q, x, m, i);
+    }
   const double g_prime = HuynhLumpedGPrimeAtOne(degree);
   for (int i = 0; i < q; ++i) {
     for (int m = 0; m < q; ++m) {
@@ -199,6 +222,7 @@ struct FaceRec {
   int holder_face, sharer_face; // local face ids
   int orientation;              // holder corner m <-> sharer corner CornerImage(o, m)
   int tag;                      // boundary section
+  bool periodic = false;        // the two sides were identified through a periodic pair
 };
 
 struct HostMesh {
@@ -208,6 +232,7 @@ struct HostMesh {
   std::vector<unsigned char> code;   // [cell][6]
   std::vector<double> coef;          // [cell][21]
   std::vector<double> c0;            // [cell][3] constant term of the map = x(0,0,0)
+  std::vector<double> h2s;           // [cell][6][3] Face::HolderToSharer of the face behind local face f
   std::vector<double> length, volume;  // local cells
   std::string error;
 
@@ -257,19 +282,20 @@ struct HostMesh {
       for (int m = 0; m < 4; ++m) { rec[m] = b[m]; rec[4 + m] = a[m]; }
       periodic[Sorted(b)] = rec;
     }
-    struct Side { int64_t cell; int face; Key nodes; };  // nodes in the cell's face order, aliased
+    struct Side { int64_t cell; int face; Key nodes; bool aliased; };  // nodes in the cell's face order, aliased
     std::map<Key, std::vector<Side>> sides;
     for (int64_t c = 0; c < nc; ++c) {
       for (int f = 0; f < 6; ++f) {
         Key k;
         for (int m = 0; m < 4; ++m) k[m] = cn[c * 8 + kFaceNodes[f][m]];
         auto it = periodic.find(Sorted(k));
-        if (it != periodic.end()) {
+        const bool aliased = it != periodic.end();
+        if (aliased) {
           for (int m = 0; m < 4; ++m)
             for (int j = 0; j < 4; ++j)
               if (k[m] == it->second[j]) { k[m] = it->second[4 + j]; break; }
         }
-        sides[Sorted(k)].push_back(Side{c, f, k});
+        sides[Sorted(k)].push_back(Side{c, f, k, aliased});
       }
     }
     nbr.assign(nc * 6, INT32_MIN);
@@ -290,7 +316,7 @@ struct HostMesh {
         int o = pi[0] + ((pi[1] == (pi[0] + 3) % 4) ? 4 : 0);
         for (int m = 0; m < 4; ++m)
           if (CornerImage(o, m) != pi[m]) { error = "face is not a square symmetry"; return false; }
-        all.push_back(FaceRec{h.cell, s.cell, h.face, s.face, o, -1});
+        all.push_back(FaceRec{h.cell, s.cell, h.face, s.face, o, -1, h.aliased || s.aliased});
       } else if (list.size() > 2) {
         error = "more than two cells share a face";
         return false;
@@ -377,6 +403,38 @@ struct HostMesh {
       volume[c] = vol;
       length[c] = std::cbrt(vol) * 0.5;
     }
+    // Face::HolderToSharer (mesh/part.hpp:118-133): between the cell centres x(0,0,0), or twice
+    // centre -> face centre on a boundary; across a periodic pair each side contributes its own
+    // centre -> face-centre vector.
+    h2s.assign(nc * 18, 0.0);
+    auto face_center = [&](int64_t c, int f, double *out) {
+      for (int d = 0; d < 3; ++d) {
+        double sum = 0;
+        for (int m = 0; m < 4; ++m) sum += xyz[cn[c * 8 + kFaceNodes[f][m]] * 3 + d];
+        out[d] = sum / 4;
+      }
+    };
+    auto set_faces = [&](std::vector<FaceRec> const &faces) {
+      for (auto const &fr : faces) {
+        double v[3];
+        if (fr.sharer < 0) {
+          face_center(fr.holder, fr.holder_face, v);
+          for (int d = 0; d < 3; ++d) v[d] = (v[d] - c0[fr.holder * 3 + d]) * 2;
+        } else if (fr.periodic) {
+          double a[3], b[3];
+          face_center(fr.holder, fr.holder_face, a);
+          face_center(fr.sharer, fr.sharer_face, b);
+          for (int d = 0; d < 3; ++d) v[d] = (a[d] - c0[fr.holder * 3 + d]) + (c0[fr.sharer * 3 + d] - b[d]);
+        } else {
+          for (int d = 0; d < 3; ++d) v[d] = c0[fr.sharer * 3 + d] - c0[fr.holder * 3 + d];
+        }
+        for (int d = 0; d < 3; ++d) {
+          h2s[(fr.holder * 6 + fr.holder_face) * 3 + d] = v[d];
+          if (fr.sharer >= 0) h2s[(fr.sharer * 6 + fr.sharer_face) * 3 + d] = v[d];
+        }
+      }
+    };
+    set_faces(local_faces); set_faces(ghost_faces); set_faces(bound_faces);
     return true;
   }
 };

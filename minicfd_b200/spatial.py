@@ -15,10 +15,10 @@ from .part import Part, cell_points
 
 class Spatial:
     def __init__(self, part: Part, *, scheme=capi.FR_LOBATTO, degree=2, riemann=capi.HLLC, device=-1,
-                 comm=None, fr_c_next=0.0):
+                 comm=None, fr_c_next=0.0, diffusion=capi.INVISCID):
         self.part = part
         self.degree = degree
-        self.ctx = capi.Context(scheme, degree, riemann, device, fr_c_next)
+        self.ctx = capi.Context(scheme, degree, riemann, device, fr_c_next, diffusion)
         self.kfields = self.ctx.kfields
         m = part.mesh
         self.ctx.set_mesh(m.nodes, part.cell_nodes, part.n_local, part.n_ghost, part.bfaces, part.btags,
@@ -69,7 +69,13 @@ class Spatial:
         self._set_bc(tag, capi.BC_SUBSONIC_OUTLET, func, time_dependent)
 
     def SetNoSlipWall(self, tag, func=None, time_dependent=False):
-        self._set_bc(tag, capi.BC_NO_SLIP_WALL, None, False)
+        """fem.hpp:219-222.  func(xyz, t) -> (unused, wall velocity u v w, normal temperature gradient),
+        demo/laminar/cavity.cpp:30-38; ignored by inviscid systems (fr/general.hpp:455-459)."""
+        self._set_bc(tag, capi.BC_NO_SLIP_WALL, func, time_dependent)
+
+    def SetDiffusion(self, beta_0, beta_1, nu, prandtl):
+        """Riemann::Diffusion::SetBetaValues + SetProperty (direct.hpp:80-83, navier_stokes.hpp:57-60)."""
+        self.ctx.set_diffusion(beta_0, beta_1, nu, prandtl)
 
     def SetInviscidWall(self, tag):
         self._set_bc(tag, capi.BC_INVISCID_WALL)

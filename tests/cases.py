@@ -7,7 +7,7 @@ import numpy as np
 from minicfd_b200 import fields, mesh
 
 # bc kinds (same numbering in refapi, oracle_check and capi)
-WALL, SUP_OUT, SUP_IN, SUB_IN, SUB_OUT, SMART = range(6)
+WALL, SUP_OUT, SUP_IN, SUB_IN, SUB_OUT, SMART, NO_SLIP = range(7)
 
 MIXED_BCS = {0: WALL, 1: SUP_OUT, 2: SUP_IN, 3: SMART, 4: SUB_OUT, 5: SUB_IN}
 SUBSONIC_INLET_STATE = [2.0, 0.0, 0.0, -1.0, 0.01]   # p_total, direction cosines (into zmax), T_total
@@ -75,3 +75,49 @@ GOLDEN_CASES = [  # (name, degree, scheme, riemann)
 ]
 GOLDEN_T = 0.25
 GOLDEN_DT = 1e-3
+
+
+# ---- Navier-Stokes with the direct-DG face flux ----------------------------------
+VISCOUS = (2.0, 1.0 / 12, 0.02, 0.708)            # beta_0, beta_1 (demo/laminar/cavity.cpp:50), nu, Prandtl
+VISCOUS_BCS = {0: NO_SLIP, 1: WALL, 2: NO_SLIP, 3: SMART, 4: SUP_OUT, 5: SUP_IN}
+WALL_VALUE = [0.0, 0.1, -0.2, 0.05, 0.3]          # (unused, wall velocity, normal temperature gradient)
+VISCOUS_GOLDEN_CASES = [("ns_p2_hllc", 2, 1), ("ns_p2_exact", 2, 0), ("ns_p3_ausm", 3, 2)]   # (name, degree, riemann)
+
+
+def apply_viscous_ref(r, kinds=VISCOUS_BCS, vis=VISCOUS):
+    import refapi
+    r.set_viscous(*vis)
+    for tag, k in kinds.items():
+        if k == NO_SLIP:
+            r.set_bc(tag, k, refapi.F_CONST, WALL_VALUE)
+        else:
+            r.set_bc(tag, k, refapi.F_SMOOTH, [SMOOTH_A])
+
+
+def apply_viscous_oracle(o, kinds=VISCOUS_BCS, vis=VISCOUS):
+    import oracle_check as oc
+    o.set_viscous(*vis)
+    for tag, k in kinds.items():
+        if k == NO_SLIP:
+            o.set_bc(tag, k, oc.F_CONST, WALL_VALUE)
+        else:
+            o.set_bc(tag, k, oc.F_SMOOTH, [SMOOTH_A])
+
+
+def viscous_bc_function(kind):
+    return fields.constant(WALL_VALUE) if kind == NO_SLIP else fields.smooth(SMOOTH_A)
+
+
+def apply_viscous_spatial(sp, kinds=VISCOUS_BCS, vis=VISCOUS):
+    sp.SetDiffusion(*vis)
+    for tag, k in kinds.items():
+        if k == NO_SLIP:
+            sp.SetNoSlipWall(tag, viscous_bc_function(k))
+        elif k == WALL:
+            sp.SetInviscidWall(tag)
+        elif k == SUP_OUT:
+            sp.SetSupersonicOutlet(tag)
+        elif k == SUP_IN:
+            sp.SetSupersonicInlet(tag, viscous_bc_function(k))
+        else:
+            sp.SetSmartBoundary(tag, viscous_bc_function(k))

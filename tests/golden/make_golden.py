@@ -33,6 +33,19 @@ def main():
         np.savez_compressed(os.path.join(HERE, name + ".npz"), u=u, residual=res, dt=dt, u_rk3=u_rk3,
                             nodes=m.nodes, cells=m.cells, bfaces=m.bfaces, btags=m.btags)
         print(name, np.linalg.norm(res), dt)
+    # fr::Lobatto on ConvectionDiffusion<rotated::Euler<..>, Direct<NavierStokes>> with no-slip walls
+    for name, degree, riemann in cases.VISCOUS_GOLDEN_CASES:
+        r = refapi.Ref(m, degree=degree, scheme=refapi.FR_VISCOUS, riemann=riemann)
+        cases.apply_viscous_ref(r)
+        u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), amp=1e-4)
+        r.set_solution(u)
+        res = r.residual(cases.GOLDEN_T)
+        dt = r.time_step(1.0, 3)
+        r.rk_update(3, 0.0, cases.GOLDEN_DT, 1)
+        u_rk3 = r.get_solution()
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), u=u, residual=res, dt=dt, u_rk3=u_rk3,
+                            nodes=m.nodes, cells=m.cells, bfaces=m.bfaces, btags=m.btags)
+        print(name, np.linalg.norm(res), dt)
 
 
 if __name__ == "__main__":

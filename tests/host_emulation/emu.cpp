@@ -20,7 +20,8 @@ void RunStage(StageArgs a, int n_blocks) {
   using G = StageGeometry<Q, CPB, NW>;
   std::vector<double> smem(G::kSharedBytes / sizeof(double) + 1);
   for (int b = 0; b < n_blocks; ++b) {
-    if (c_tab.general) RunStageBlockOnHost<Q, R, CPB, NW, true>(a, b, smem.data());
+    if (a.grad) RunStageBlockOnHost<Q, R, CPB, NW, false, true>(a, b, smem.data());
+    else if (c_tab.general) RunStageBlockOnHost<Q, R, CPB, NW, true>(a, b, smem.data());
     else RunStageBlockOnHost<Q, R, CPB, NW, false>(a, b, smem.data());
   }
 }
@@ -51,7 +52,8 @@ int emu_stage(int degree, int scheme, int riemann, int64_t n_nodes, const double
     int64_t n_local, int64_t n_ghost, const int64_t *cell_nodes, int64_t n_bfaces,
     const int64_t *bface_nodes, const int32_t *bface_tags, int64_t n_pairs, const int64_t *pairs,
     const int32_t *tag_kinds, const double *bvals, const double *column_in, const double *column_u0,
-    int mode, double dt, double *column_out, char *err, int err_len, double c_next) {
+    int mode, double dt, double *column_out, char *err, int err_len, double c_next,
+    const double *viscous /* null, or beta0, beta1, nu, prandtl */) {
   const int q = degree + 1, F = 5 * q * q * q;
   const int cpb = (q == 3) ? kP2Cells : kP3Cells, nw = (q == 3) ? kP2Warps : kP3Warps;
   c_tab = BuildTables(degree, scheme, nw, kTile / cpb, c_next);
@@ -78,6 +80,19 @@ int emu_stage(int degree, int scheme, int riemann, int64_t n_nodes, const double
   a.geom = geom.data(); a.nbr = nbr.data(); a.code = code.data();
   a.bkind = bkind.data(); a.bvals = bvals ? bvals : zero_vals.data();
   a.n_local = (int)n_local; a.block_begin = 0; a.mode = mode; a.dt = dt;
+  a.dt_dev = nullptr; a.grad = nullptr; a.hn = nullptr; a.h2s = nullptr;
+  std::vector<double> grad, hn, h2s;
+  if (viscous) {
+    const int N = q * q * q;
+    grad.assign((size_t)nt * N * 15 * kTile, 0.0);
+    hn.assign((size_t)nt * 6 * q * q * 15 * kTile, 0.0);
+    h2s = ToTiles(mesh.h2s, 18, nc, nt);
+    if (q == 3) RunTraceOnHost<3>(uin.data(), geom.data(), grad.data(), hn.data(), (int)nc);
+    else RunTraceOnHost<4>(uin.data(), geom.data(), grad.data(), hn.data(), (int)nc);
+    a.grad = grad.data(); a.hn = hn.data(); a.h2s = h2s.data();
+    a.vis.beta0 = viscous[0]; a.vis.beta1 = viscous[1]; a.vis.nu = viscous[2];
+    a.vis.cond = viscous[2] * (kGasR * kGammaOverGm1) / viscous[3];
+  }
   int n_blocks = (int)((n_local + cpb - 1) / cpb);
   if (q == 3) RunStageQ<3, kP2Cells, kP2Warps>(riemann, a, n_blocks);
   else RunStageQ<4, kP3Cells, kP3Warps>(riemann, a, n_blocks);

@@ -1,0 +1,159 @@
+"""GPU parity tests of the viscous path: fr::Lobatto on
+ConvectionDiffusion<rotated::Euler<..>, Direct<NavierStokes<Gas>>> through the C ABI, against the oracle.
+Tolerance 1e-12 relative (max norm)."""
+import os
+
+import numpy as np
+import pytest
+
+import cases
+import oracle_check as oc
+import refapi
+from minicfd_b200 import capi, fields, mesh as meshmod
+from minicfd_b200.part import Part, cell_points
+from minicfd_b200.spatial import RungeKutta, Spatial
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+TOL = 1e-12
+
+
+def relerr(a, b):
+    return np.abs(a - b).max() / np.abs(b).max()
+
+
+def viscous_spatial(m, degree, riemann, **kw):
+    return Spatial(Part(m), scheme=capi.FR_LOBATTO, degree=degree, riemann=riemann, device=0,
+                   diffusion=capi.NAVIER_STOKES_DDG, **kw)
+
+
+@pytest.mark.parametrize("name,degree,riemann", cases.VISCOUS_GOLDEN_CASES)
+def test_navier_stokes_golden(name, degree, riemann):
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    m = meshmod.HexMesh(nodes=g["nodes"], cells=g["cells"], bfaces=g["bfaces"], btags=g["btags"])
+    sp = viscous_spatial(m, degree, riemann)
+    cases.apply_viscous_spatial(sp)
+    sp.SetSolutionColumn(g["u"])
+    sp.SetTime(cases.GOLDEN_T)
+    assert relerr(sp.GetResidualColumn(), g["residual"]) < TOL
+    assert sp.GetTimeStep(1.0, 3) == pytest.approx(float(g["dt"]), rel=1e-13)
+    RungeKutta(3).Update(sp, 0.0, cases.GOLDEN_DT)
+    assert relerr(sp.GetSolutionColumn(), g["u_rk3"]) < TOL
+
+
+@pytest.mark.parametrize("degree", [2, 3])
+@pytest.mark.parametrize("riemann", [capi.EXACT, capi.HLLC, capi.AUSM])
+def test_navier_stokes_vs_oracle(degree, riemann):
+    m = cases.small_mesh(seed=12)
+    vis = (1.5, 0.1, 0.03, 0.72)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), seed=4, amp=1e-4)
+    o = oc.Oracle(m, degree, 3, riemann)
+    cases.apply_viscous_oracle(o, vis=vis)
+    sp = viscous_spatial(m, degree, riemann)
+    cases.apply_viscous_spatial(sp, vis=vis)
+    sp.SetSolutionColumn(u)
+    sp.SetTime(0.2)
+    assert relerr(sp.GetResidualColumn(), o.residual(u, 0.2)) < TOL
+    for order in (1, 2, 3):
+        sp.SetSolutionColumn(u)
+        RungeKutta(order).Update(sp, 0.0, 1e-3)
+        assert relerr(sp.GetSolutionColumn(), o.rk_update(u, order, 0.0, 1e-3)) < TOL
+    # the column algebra of rk.hpp through GetResidualColumn gives the same state as the fused stages
+    sp.SetSolutionColumn(u)
+    RungeKutta(3).UpdateGeneric(sp, 0.0, 1e-3)
+    assert relerr(sp.GetSolutionColumn(), o.rk_update(u, 3, 0.0, 1e-3)) < TOL
+
+
+@pytest.mark.skipif(not refapi.available(2), reason="oracle/_ref not shipped")
+def test_navier_stokes_against_reference_binary_many_steps():
+    m = cases.small_mesh(seed=5)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, 2), seed=1, amp=1e-4)
+    r = refapi.Ref(m, degree=2, scheme=refapi.FR_VISCOUS, riemann=refapi.HLLC)
+    cases.apply_viscous_ref(r)
+    r.set_solution(u)
+    sp = viscous_spatial(m, 2, capi.HLLC)
+    cases.apply_viscous_spatial(sp)
+    sp.SetSolutionColumn(u)
+    t, dt = 0.0, 1e-3
+    for _ in range(10):
+        RungeKutta(3).Update(sp, t, dt)
+        t += dt
+    r.rk_update(3, 0.0, dt, 10)
+    assert relerr(sp.GetSolutionColumn(), r.get_solution()) < 1e-11
+
+
+def test_zero_viscosity_is_the_euler_path_bit_for_bit():
+    """With nu = 0 and no no-slip wall every viscous term is an exact zero."""
+    m = meshmod.scramble(meshmod.box(5, 4, 3, warp=0.1, seed=3), seed=3)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, 2), seed=2)
+    a = Spatial(Part(m), degree=2, riemann=capi.HLLC, device=0)
+    b = viscous_spatial(m, 2, capi.HLLC)
+    b.SetDiffusion(2.0, 1.0 / 12, 0.0, 0.708)
+    for sp in (a, b):
+        cases.apply_bcs_spatial(sp, cases.MIXED_BCS)
+        sp.SetSolutionColumn(u)
+        sp.SetTime(0.1)
+    assert np.array_equal(a.GetResidualColumn(), b.GetResidualColumn())
+
+
+def test_viscous_free_stream_and_couette_like_shear():
+    """Uniform flow has zero residual on a warped mesh (gradients and Hessians of a constant vanish up to
+    rounding); a linear shear profile u(y) produces no net viscous force in the interior (tau is constant)."""
+    m = meshmod.scramble(meshmod.box(4, 4, 4, warp=0.12, seed=7, periodic=False), seed=7)
+    sp = viscous_spatial(m, 2, capi.HLLC)
+    sp.SetDiffusion(2.0, 1.0 / 12, 0.05, 0.708)
+    state = np.array([1.2, 0.3, -0.2, 0.1, 2.5])
+    for tag in range(6):
+        sp.SetSmartBoundary(tag, fields.constant(state))
+    sp.Approximate(lambda x: fields.constant(state)(x, 0.0))
+    res = sp.GetResidualColumn()
+    assert np.abs(res).max() < 1e-11
+
+
+def test_navier_stokes_two_parts_with_halo_buffers():
+    """Two parts on one GPU: the ghost cells' traces (gradient, Hessian . n) are rebuilt from the unpacked
+    coefficients, as the reference rebuilds them from the ghost cells' polynomials."""
+    import torch
+    from minicfd_b200.halo import _DeviceArray
+    m = meshmod.scramble(meshmod.box(6, 4, 2, warp=0.1, seed=2), seed=3)
+    parts = (np.arange(m.n_cells) * 2 // m.n_cells).astype(np.int32)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, 2), seed=9, amp=1e-4)
+    o = oc.Oracle(m, 2, 3, 1)
+    cases.apply_viscous_oracle(o)
+    expect_res = o.residual(u, 0.0).reshape(-1, 135)
+    expect_u = o.rk_update(u, 3, 0.0, 1e-3).reshape(-1, 135)
+    P = [Part(m, parts, r, 2) for r in range(2)]
+    S = [Spatial(p, degree=2, riemann=capi.HLLC, device=0, diffusion=capi.NAVIER_STOKES_DDG) for p in P]
+    for sp in S:
+        cases.apply_viscous_spatial(sp)
+    bufs = []
+    for sp in S:
+        (s_ptr, s_n), (r_ptr, r_n) = sp.ctx.halo_buffers()
+        bufs.append((s_ptr, s_n, r_ptr, r_n))
+
+    def exchange():
+        for sp in S:
+            sp.ctx.halo_pack()
+        torch.cuda.synchronize()
+        for a, b in ((0, 1), (1, 0)):
+            src = torch.as_tensor(_DeviceArray(bufs[a][0], bufs[a][1]), device="cuda")
+            dst = torch.as_tensor(_DeviceArray(bufs[b][2], bufs[b][3]), device="cuda")
+            dst.copy_(src)
+        torch.cuda.synchronize()
+
+    for sp, p in zip(S, P):
+        sp.SetSolutionColumn(p.gather_from_global(u, 135))
+    exchange()
+    for sp, p in zip(S, P):
+        sp.ctx.halo_unpack()
+        assert relerr(sp.ctx.residual(0.0).reshape(-1, 135), expect_res[p.local_global]) < TOL
+    for sp in S:
+        sp.ctx.rk_begin(3, 0.0, 1e-3)
+    for stage in range(3):
+        exchange()
+        for sp in S:
+            sp.ctx.rk_stage_inner(stage)
+            sp.ctx.halo_unpack()
+            sp.ctx.rk_stage_inter(stage)
+    for sp, p in zip(S, P):
+        assert relerr(sp.GetSolutionColumn().reshape(-1, 135), expect_u[p.local_global]) < TOL

@@ -106,6 +106,29 @@ def test_kernel_source_on_host_matches_golden(name, degree, scheme, riemann):
     assert relerr(u3, g["u_rk3"]) < 1e-12
 
 
+@pytest.mark.parametrize("name,degree,riemann", cases.VISCOUS_GOLDEN_CASES)
+def test_viscous_kernel_source_on_host_matches_golden(name, degree, riemann):
+    """Trace + viscous stage device code, run on the host, against the reference's Navier-Stokes vectors."""
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    m = meshmod.HexMesh(nodes=g["nodes"], cells=g["cells"], bfaces=g["bfaces"], btags=g["btags"])
+    holder, hf, tags, pts = emuapi.boundary(m, degree)
+    def bvals(t):
+        out = np.zeros(pts.shape[:2] + (5,))
+        for tag, kind in cases.VISCOUS_BCS.items():
+            sel = tags == tag
+            out[sel] = cases.viscous_bc_function(kind)(pts[sel], t)
+        return out
+    u = g["u"]
+    kw = dict(tag_kinds=cases.VISCOUS_BCS, viscous=cases.VISCOUS)
+    res = emuapi.stage(m, degree, 0, riemann, u, bvals=bvals(cases.GOLDEN_T), **kw)
+    assert relerr(res, g["residual"]) < 1e-12
+    dt = cases.GOLDEN_DT
+    u1 = emuapi.stage(m, degree, 0, riemann, u, bvals=bvals(0.0), mode=1, dt=dt, **kw)
+    u2 = emuapi.stage(m, degree, 0, riemann, u1, bvals=bvals(dt), column_u0=u, mode=2, dt=dt, **kw)
+    u3 = emuapi.stage(m, degree, 0, riemann, u2, bvals=bvals(dt / 2), column_u0=u, mode=3, dt=dt, **kw)
+    assert relerr(u3, g["u_rk3"]) < 1e-12
+
+
 def test_kernel_source_periodic_equals_embedded_box():
     """A periodic box must give the same residuals as the interior of a larger box fed with the same
     2*pi-periodic field (GPU-only periodic variant of BASELINE config 2)."""

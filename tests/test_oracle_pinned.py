@@ -61,6 +61,40 @@ def test_c_oracle_matches_reference(degree, scheme, riemann):
         assert relerr(o.rk_update(u, order, 0.0, 2e-3), r.get_solution()) < TOL
 
 
+@pytest.mark.parametrize("name,degree,riemann", cases.VISCOUS_GOLDEN_CASES)
+def test_c_oracle_viscous_matches_golden(name, degree, riemann):
+    """Navier-Stokes + direct DG with no-slip walls against the reference's vectors."""
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    o = oc.Oracle(_golden_mesh(g), degree, 3, riemann)
+    cases.apply_viscous_oracle(o)
+    assert relerr(o.residual(g["u"], cases.GOLDEN_T), g["residual"]) < TOL
+    assert o.time_step(g["u"], 1.0, 3) == pytest.approx(float(g["dt"]), rel=1e-14)
+    assert relerr(o.rk_update(g["u"], 3, 0.0, cases.GOLDEN_DT), g["u_rk3"]) < TOL
+
+
+@pytest.mark.skipif(not refapi.available(2), reason="oracle/_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("degree,riemann,nu", [(2, 1, 0.05), (2, 0, 1e-3), (3, 2, 0.02), (3, 1, 0.0)])
+def test_c_oracle_viscous_matches_reference(degree, riemann, nu):
+    m = meshmod.scramble(meshmod.box(3, 2, 2, warp=0.2, seed=11), seed=5)
+    vis = (1.5, 0.1, nu, 0.72)
+    r = refapi.Ref(m, degree=degree, scheme=refapi.FR_VISCOUS, riemann=riemann)
+    o = oc.Oracle(m, degree, 3, riemann)
+    cases.apply_viscous_ref(r, vis=vis)
+    cases.apply_viscous_oracle(o, vis=vis)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), seed=7, amp=1e-4)
+    r.set_solution(u)
+    assert relerr(o.residual(u, 0.1), r.residual(0.1)) < TOL
+    r.rk_update(3, 0.0, 1e-3, 1)
+    assert relerr(o.rk_update(u, 3, 0.0, 1e-3), r.get_solution()) < TOL
+    if nu == 0.0:   # without viscosity and without no-slip walls the Euler residual must come back
+        kinds = {t: (cases.WALL if k == cases.NO_SLIP else k) for t, k in cases.VISCOUS_BCS.items()}
+        o0 = oc.Oracle(m, degree, 0, riemann)
+        cases.apply_viscous_oracle(o0, kinds=kinds, vis=vis)
+        o3 = oc.Oracle(m, degree, 3, riemann)
+        cases.apply_viscous_oracle(o3, kinds=kinds, vis=vis)
+        assert np.array_equal(o0.residual(u, 0.1), o3.residual(u, 0.1))
+
+
 def _flux_1d(rho, u, p):
     """Flux of a 1-D primitive state (test/riemann/euler/exact.cpp:34-39)."""
     e = p / 0.4 + 0.5 * rho * u * u
