@@ -140,11 +140,52 @@ struct Euler {  // rotated/euler.hpp:23-40
   static constexpr int kComponents = 5;
   static constexpr int kDimensions = 3;
   static constexpr int kKind = Unrotated::kKind;
+  static constexpr int kDiffusion = MCFD_INVISCID;
   using Conservative = euler::Conservatives<Scalar, 3>;
   using Primitive = euler::Primitives<Scalar, 3>;
   using Value = algebra::Vector<Scalar, 5>;
 };
 }  // namespace rotated
+
+namespace diffusive {
+// riemann/diffusive/navier_stokes.hpp:20-228 as a tag: the class-static property (:54-63) is kept here and
+// handed to the context before every residual evaluation (mcfd_set_diffusion).
+template <class G>
+struct NavierStokes {
+  using Gas = G;
+  using Scalar = typename Gas::Scalar;
+  static constexpr int kComponents = 5;
+  static constexpr int kDimensions = 3;
+  struct Property { Scalar nu, prandtl; };
+  static void SetProperty(Scalar nu, Scalar prandtl) { property_ = Property{nu, prandtl}; }
+  static Property const &GetProperty() { return property_; }
+  inline static Property property_{0.0, 0.708};
+};
+// riemann/diffusive/direct.hpp:15-91
+template <class DiffusionModel>
+struct Direct : DiffusionModel {
+  using Diffusion = Direct;
+  using Scalar = typename DiffusionModel::Scalar;
+  static void SetBetaValues(Scalar beta_0, Scalar beta_1) { beta_0_ = beta_0; beta_1_ = beta_1; }
+  inline static Scalar beta_0_ = 2.0, beta_1_ = 1.0 / 12;
+};
+}  // namespace diffusive
+
+// riemann/concept.hpp:93-121
+template <class C, class D>
+struct ConvectionDiffusion : C, D {
+  using Convection = C;
+  using Diffusion = D;
+  using Scalar = typename C::Scalar;
+  using Gas = typename C::Gas;
+  using Conservative = typename C::Conservative;
+  using Primitive = typename C::Primitive;
+  using Value = typename C::Value;
+  static constexpr int kComponents = C::kComponents;
+  static constexpr int kDimensions = C::kDimensions;
+  static constexpr int kKind = C::kKind;
+  static constexpr int kDiffusion = MCFD_NAVIER_STOKES_DDG;
+};
 }  // namespace riemann
 
 namespace b200 {
@@ -329,7 +370,7 @@ class FiniteElementB200 : public temporal::System<typename P::Scalar> {
   using Function = std::function<Value(const Global &, double)>;  // fem.hpp:72
 
   explicit FiniteElementB200(Part *part_ptr, int device = -1, double c_next = 0.0) : part_ptr_(part_ptr) {
-    mcfd_config cfg{kScheme, Part::kDegrees, Riemann::kKind, device, c_next};
+    mcfd_config cfg{kScheme, Part::kDegrees, Riemann::kKind, device, c_next, Riemann::kDiffusion, 0};
     if (mcfd_create(&cfg, &ctx_) != 0) throw std::runtime_error(std::string("mcfd_create: ") + mcfd_last_error(nullptr));
     auto &p = *part_ptr_;
     b200::Check(mcfd_set_mesh(ctx_, (int64_t)p.nodes_.size() / 3, p.nodes_.data(), p.n_local_, p.n_ghost_,
@@ -368,7 +409,8 @@ class FiniteElementB200 : public temporal::System<typename P::Scalar> {
   template <typename F> void SetSupersonicInlet(const std::string &name, F &&f) { SetBc(name, MCFD_BC_SUPERSONIC_INLET, f); }
   template <typename F> void SetSubsonicInlet(const std::string &name, F &&f) { SetBc(name, MCFD_BC_SUBSONIC_INLET, f); }
   template <typename F> void SetSubsonicOutlet(const std::string &name, F &&f) { SetBc(name, MCFD_BC_SUBSONIC_OUTLET, f); }
-  template <typename F> void SetNoSlipWall(const std::string &name, F &&) { SetBc(name, MCFD_BC_NO_SLIP_WALL, Function()); }
+  // ignored by inviscid Riemann types, like the reference (fr/general.hpp:455-459)
+  template <typename F> void SetNoSlipWall(const std::string &name, F &&f) { SetBc(name, MCFD_BC_NO_SLIP_WALL, f); }
   void SetInviscidWall(const std::string &name) { SetBc(name, MCFD_BC_INVISCID_WALL, Function()); }
   void SetSupersonicOutlet(const std::string &name) { SetBc(name, MCFD_BC_SUPERSONIC_OUTLET, Function()); }
 
@@ -384,11 +426,13 @@ class FiniteElementB200 : public temporal::System<typename P::Scalar> {
   }
   Column GetResidualColumn() const override {
     Column column(part().GetCellDataSize());
+    PushDiffusion();
     b200::Check(mcfd_residual(ctx_, t_curr_, column.data(), nullptr), ctx_, "mcfd_residual");
     return column;
   }
   bool FusedUpdate(int order, double t_curr, double dt) override {
     if (part().CountGhostCells() > 0) return false;   // parts with ghosts are driven stage by stage
+    PushDiffusion();
     b200::Check(mcfd_rk_step(ctx_, order, t_curr, dt), ctx_, "mcfd_rk_step");
     return true;
   }
@@ -399,6 +443,14 @@ class FiniteElementB200 : public temporal::System<typename P::Scalar> {
   }
 
  private:
+  // the reference reads its class statics at every flux evaluation; hand their current values over
+  void PushDiffusion() const {
+    if constexpr (Riemann::kDiffusion != MCFD_INVISCID) {
+      using D = typename Riemann::Diffusion;
+      b200::Check(mcfd_set_diffusion(ctx_, D::beta_0_, D::beta_1_, D::GetProperty().nu, D::GetProperty().prandtl),
+          ctx_, "mcfd_set_diffusion");
+    }
+  }
   struct Bc { Function func; std::vector<double> points, values; };
   void SetBc(const std::string &name, int kind, Function func) {
     int32_t tag = part().TagOf(name);

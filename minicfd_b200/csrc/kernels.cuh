@@ -35,7 +35,18 @@ constexpr int kMaxWarps = 16;
 #ifndef MCFD_P2_MINB
 #define MCFD_P2_MINB 2
 #endif
+// the viscous instantiation carries more live state per face point: its own launch shape
+#ifndef MCFD_P2_VWARPS
+#define MCFD_P2_VWARPS 12
+#endif
+#ifndef MCFD_P2_VMINB
+#define MCFD_P2_VMINB 1
+#endif
+#ifndef MCFD_TRACE_MINB
+#define MCFD_TRACE_MINB 2
+#endif
 constexpr int kP2Cells = MCFD_P2_CELLS, kP2Warps = MCFD_P2_WARPS, kP3Cells = 16, kP3Warps = 16;
+constexpr int kP2ViscousWarps = MCFD_P2_VWARPS;
 
 // Per-degree tables, filled by the host (tables.cpp) and copied to constant memory.
 struct Tables {
@@ -707,7 +718,7 @@ MCFD_HD void StagePhaseC(const StageArgs &p, int tid, int bid, double *smem,
 // host, where RunStageBlockOnHost() below replays the phases thread by thread.
 #ifdef __CUDACC__
 template <int Q, int kRiemann, int CPB, int NW, bool kGeneral, bool kViscous = false>
-__global__ void __launch_bounds__(NW * 32, (Q == 3 && !kViscous ? MCFD_P2_MINB : 1))
+__global__ void __launch_bounds__(NW * 32, (Q == 3 ? (kViscous ? MCFD_P2_VMINB : MCFD_P2_MINB) : 1))
 StageKernel(StageArgs p) {
   extern __shared__ double smem[];
   const int tid = threadIdx.x, bid = blockIdx.x;
@@ -754,21 +765,36 @@ void RunStageBlockOnHost(const StageArgs &p, int bid, double *smem) {
 // geometry staged in shared memory, lanes = cells, nodes dealt to the warps.
 template <int Q>
 struct TraceShape {
-  static constexpr int N = Q * Q * Q, F = 5 * N, NW = 8;
+  static constexpr int N = Q * Q * Q, F = 5 * N;
+#ifndef MCFD_TRACE_WARPS
+#define MCFD_TRACE_WARPS 4
+#endif
+  static constexpr int NW = MCFD_TRACE_WARPS;     // small CTAs, several per SM: one stages while another computes
   static constexpr size_t kSharedBytes = (size_t)(F + kGeomRows) * kTile * sizeof(double);
 };
 #ifdef __CUDACC__
 template <int Q>
-__global__ void __launch_bounds__(256, 1) TraceKernel(const double *u, const double *geom, double *grad,
-    double *hn, int tile_begin, int cell_begin, int cell_end) {
+__global__ void __launch_bounds__(TraceShape<Q>::NW * 32, MCFD_TRACE_MINB) TraceKernel(const double *u,
+    const double *geom, double *grad, double *hn, int tile_begin, int cell_begin, int cell_end) {
   using S = TraceShape<Q>;
+  constexpr int T = S::NW * 32;
   extern __shared__ double smem[];
   double *sU = smem, *sG = smem + S::F * kTile;
   const int tile = tile_begin + blockIdx.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const double *src = u + (size_t)tile * S::F * kTile;
-  for (int i = threadIdx.x; i < S::F * kTile; i += S::NW * 32) sU[i] = src[i];
-  for (int i = threadIdx.x; i < kGeomRows * kTile; i += S::NW * 32) sG[i] = geom[(size_t)tile * kGeomRows * kTile + i];
+  {  // stage the tile: batches of independent 16-byte loads, then the stores
+    const double2 *src = reinterpret_cast<const double2 *>(u + (size_t)tile * S::F * kTile);
+    double2 *dst = reinterpret_cast<double2 *>(sU);
+    constexpr int kVec = S::F * kTile / 2, kBatch = 6;
+    for (int base = threadIdx.x; base < kVec; base += T * kBatch) {
+      double2 r[kBatch];
+#pragma unroll
+      for (int j = 0; j < kBatch; ++j) if (base + j * T < kVec) r[j] = src[base + j * T];
+#pragma unroll
+      for (int j = 0; j < kBatch; ++j) if (base + j * T < kVec) dst[base + j * T] = r[j];
+    }
+    for (int i = threadIdx.x; i < kGeomRows * kTile; i += T) sG[i] = geom[(size_t)tile * kGeomRows * kTile + i];
+  }
   __syncthreads();
   const int cell = tile * kTile + lane;
   if (cell < cell_begin || cell >= cell_end) return;

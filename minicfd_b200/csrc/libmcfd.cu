@@ -106,7 +106,6 @@ cudaError_t LaunchStageG(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
 // the general Vincent correction (fr::General) is a separate instantiation: the lumped schemes pay nothing
 template <int Q, int R, int CPB, int NW>
 cudaError_t LaunchStageT(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
-  if (ctx->cfg.diffusion == MCFD_NAVIER_STOKES_DDG) return LaunchStageG<Q, R, CPB, NW, false, true>(ctx, a, n_blocks);
   return ctx->cfg.scheme == MCFD_FR_GENERAL ? LaunchStageG<Q, R, CPB, NW, true>(ctx, a, n_blocks)
                                             : LaunchStageG<Q, R, CPB, NW, false>(ctx, a, n_blocks);
 }
@@ -120,6 +119,15 @@ cudaError_t LaunchStageQ(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
   }
 }
 
+template <int Q, int CPB, int NW>
+cudaError_t LaunchStageViscous(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
+  switch (ctx->cfg.riemann) {
+  case MCFD_EXACT: return LaunchStageG<Q, kExact, CPB, NW, false, true>(ctx, a, n_blocks);
+  case MCFD_HLLC: return LaunchStageG<Q, kHllc, CPB, NW, false, true>(ctx, a, n_blocks);
+  default: return LaunchStageG<Q, kAusm, CPB, NW, false, true>(ctx, a, n_blocks);
+  }
+}
+
 // Viscous traces (gradient at the nodes, Hessian . normal at the face points) of cells
 // [cell_begin, cell_end) of the state `u`.
 int LaunchTrace(mcfd_ctx *ctx, const double *u, int64_t cell_begin, int64_t cell_end) {
@@ -127,7 +135,7 @@ int LaunchTrace(mcfd_ctx *ctx, const double *u, int64_t cell_begin, int64_t cell
   const int tile_begin = (int)(cell_begin / kTile), tile_end = (int)((cell_end + kTile - 1) / kTile);
   cudaError_t e;
   if (ctx->q == 3) {
-    TraceKernel<3><<<tile_end - tile_begin, 256, TraceShape<3>::kSharedBytes, ctx->stream>>>(u, ctx->geom.p,
+    TraceKernel<3><<<tile_end - tile_begin, TraceShape<3>::NW * 32, TraceShape<3>::kSharedBytes, ctx->stream>>>(u, ctx->geom.p,
         ctx->grad.p, ctx->hn.p, tile_begin, (int)cell_begin, (int)cell_end);
     e = cudaGetLastError();
   } else {
@@ -138,7 +146,7 @@ int LaunchTrace(mcfd_ctx *ctx, const double *u, int64_t cell_begin, int64_t cell
       if (e != cudaSuccess) return Fail(ctx, MCFD_ERR_CUDA, cudaGetErrorString(e));
       configured = true;
     }
-    kernel<<<tile_end - tile_begin, 256, TraceShape<4>::kSharedBytes, ctx->stream>>>(u, ctx->geom.p, ctx->grad.p,
+    kernel<<<tile_end - tile_begin, TraceShape<4>::NW * 32, TraceShape<4>::kSharedBytes, ctx->stream>>>(u, ctx->geom.p, ctx->grad.p,
         ctx->hn.p, tile_begin, (int)cell_begin, (int)cell_end);
     e = cudaGetLastError();
   }
@@ -173,8 +181,14 @@ int LaunchStage(mcfd_ctx *ctx, const double *u_in, const double *u0, double *u_o
     ctx->events_used++;
     MCFD_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
   }
-  cudaError_t e = (ctx->q == 3) ? LaunchStageQ<3, kP2Cells, kP2Warps>(ctx, a, n_blocks)
-                                : LaunchStageQ<4, kP3Cells, kP3Warps>(ctx, a, n_blocks);
+  cudaError_t e;
+  if (ctx->cfg.diffusion != MCFD_INVISCID) {
+    e = (ctx->q == 3) ? LaunchStageViscous<3, kP2Cells, kP2ViscousWarps>(ctx, a, n_blocks)
+                      : LaunchStageViscous<4, kP3Cells, kP3Warps>(ctx, a, n_blocks);
+  } else {
+    e = (ctx->q == 3) ? LaunchStageQ<3, kP2Cells, kP2Warps>(ctx, a, n_blocks)
+                      : LaunchStageQ<4, kP3Cells, kP3Warps>(ctx, a, n_blocks);
+  }
   if (e != cudaSuccess) return Fail(ctx, MCFD_ERR_CUDA, std::string("stage kernel: ") + cudaGetErrorString(e));
   if (ctx->timing) MCFD_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
   ctx->launches++;
@@ -277,7 +291,7 @@ int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
   ctx->n_nodes = ctx->q * ctx->q * ctx->q;
   ctx->fields = 5 * ctx->n_nodes;
   ctx->cpb = (ctx->q == 3) ? kP2Cells : kP3Cells;
-  ctx->n_warps = (ctx->q == 3) ? kP2Warps : kP3Warps;
+  ctx->n_warps = (ctx->q == 3) ? (config->diffusion != MCFD_INVISCID ? kP2ViscousWarps : kP2Warps) : kP3Warps;
   ctx->tables = BuildTables(config->degree, config->scheme, ctx->n_warps, kTile / ctx->cpb, config->fr_c_next);
   e = cudaMemcpyToSymbol(c_tab, &ctx->tables, sizeof(Tables));
   if (e != cudaSuccess) return Fail(nullptr, MCFD_ERR_CUDA, cudaGetErrorString(e));

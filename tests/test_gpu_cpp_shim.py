@@ -75,3 +75,57 @@ def test_sod_driver_through_cpp_template_api(tmp_path, flag, riemann, tol):
     # Exact: the reference's Newton stop test (1e-8) makes its own flux only that accurate; a 1-ulp
     # difference in pow() may change its iteration count, hence the looser bound.
     assert np.abs(got - ref).max() / np.abs(ref).max() < tol
+
+
+def _cavity_reference(n, n_steps):
+    """demo/laminar/cavity.cpp's loop on the CPU checker (Navier-Stokes + direct DG, no-slip walls)."""
+    m = meshmod.box(n, n, 2, hi=(1.0, 1.0, 0.25))
+    ic = [1.0, 0, 0, 0, (1.0 / (1.4 * 0.04)) / 0.4]
+    moving, fixed = [0, 1.0, 0, 0, 0], [0, 0, 0, 0, 0]
+    walls = {meshmod.XMIN: fixed, meshmod.XMAX: fixed, meshmod.YMIN: fixed, meshmod.YMAX: moving}
+    if refapi.available(2):
+        r = refapi.Ref(m, degree=2, scheme=refapi.FR_VISCOUS, riemann=1)
+        r.set_viscous(2.0, 1.0 / 12, 0.01, 0.708)
+        for tag, val in walls.items():
+            r.set_bc(tag, refapi.NO_SLIP, refapi.F_CONST, val)
+        for tag in (meshmod.ZMIN, meshmod.ZMAX):
+            r.set_bc(tag, refapi.WALL)
+        r.approximate(refapi.F_CONST, ic)
+        t = 0.0
+        for _ in range(n_steps):
+            dt = r.time_step(1e-3, 3)
+            r.rk_update(3, t, dt, 1)
+            t += dt
+        return r.get_solution()
+    o = oc.Oracle(m, 2, 3, 1)
+    o.set_viscous(2.0, 1.0 / 12, 0.01, 0.708)
+    for tag, val in walls.items():
+        o.set_bc(tag, 6, oc.F_CONST, val)
+    for tag in (meshmod.ZMIN, meshmod.ZMAX):
+        o.set_bc(tag, 0)
+    u = o.approximate(oc.F_CONST, ic)
+    t = 0.0
+    for _ in range(n_steps):
+        dt = o.time_step(u, 1e-3, 3)
+        u = o.rk_update(u, 3, t, dt)
+        t += dt
+    return u
+
+
+def test_lid_driven_cavity_driver_through_cpp_template_api(tmp_path):
+    """ConvectionDiffusion<rotated::Euler<HLLC>, Direct<NavierStokes>> named exactly as demo/laminar/shockless.hpp
+    names it; SetBetaValues / SetProperty / SetNoSlipWall as demo/laminar/cavity.cpp calls them."""
+    exe = tmp_path / "cavity"
+    subprocess.check_call(["g++", "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "demo", "laminar", "cavity.cpp"), "-o", str(exe),
+                           "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200",
+                           "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")])
+    out = tmp_path / "column.bin"
+    n, n_steps = 6, 10
+    res = subprocess.run([str(exe), str(n_steps), str(out), str(n)], capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout + res.stderr
+    got = np.fromfile(out, dtype=np.float64)
+    ref = _cavity_reference(n, n_steps)
+    assert got.shape == ref.shape == (n * n * 2 * 135,)
+    assert np.abs(got[1::5]).max() > 1e-4      # the lid has set the fluid in motion
+    assert np.abs(got - ref).max() / np.abs(ref).max() < 1e-12
