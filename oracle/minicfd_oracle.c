@@ -1011,6 +1011,206 @@ void oracle_limiter(void *h, int kind, double *u) {
   }
 }
 
+/* ---- weno::Lazy on Extrapolation<Hexahedron> -------------------------------------- */
+#define MAXM 20
+static int taylor_count(int degree) { return degree == 2 ? 10 : 20; } /* basis/taylor.hpp:27-31 */
+static void taylor_values(int degree, const double *d, double *t) { /* basis/taylor.hpp:204-218 */
+  double x = d[0], y = d[1], z = d[2];
+  t[0] = 1; t[1] = x; t[2] = y; t[3] = z;
+  t[4] = x * x; t[5] = x * y; t[6] = x * z; t[7] = y * y; t[8] = y * z; t[9] = z * z;
+  if (degree == 3) {
+    t[10] = x * t[4]; t[11] = x * t[5]; t[12] = x * t[6]; t[13] = x * t[7]; t[14] = x * t[8]; t[15] = x * t[9];
+    t[16] = y * t[7]; t[17] = y * t[8]; t[18] = y * t[9]; t[19] = z * t[9];
+  }
+}
+/* Taylor::GetPartialDerivatives for one component (basis/taylor.hpp:241-372): entry i is the partial
+   derivative named by Taylor index i, entry 0 is zero */
+static void taylor_partial_derivatives(int degree, const double *d, const double *c, double *r) {
+  double x = d[0], y = d[1], z = d[2];
+  int m = taylor_count(degree);
+  for (int i = 0; i < m; ++i) r[i] = c[i];
+  r[0] = 0;
+  r[1] += c[4] * (2 * x) + c[5] * y + c[6] * z;
+  r[2] += c[5] * x + c[7] * (2 * y) + c[8] * z;
+  r[3] += c[6] * x + c[8] * y + c[9] * (2 * z);
+  if (degree == 2) {
+    r[4] += c[4]; r[7] += c[7]; r[9] += c[9];
+    return;
+  }
+  double xx = x * x, xy = x * y, xz = x * z, yy = y * y, yz = y * z, zz = z * z;
+  r[1] += c[10] * (3 * xx) + c[11] * (2 * xy) + c[12] * (2 * xz) + c[13] * yy + c[14] * yz + c[15] * zz;
+  r[2] += c[11] * xx + c[14] * xz + c[13] * (2 * xy) + c[16] * (3 * yy) + c[17] * (2 * yz) + c[18] * zz;
+  r[3] += c[12] * xx + c[14] * xy + c[15] * (2 * xz) + c[17] * yy + c[18] * (2 * yz) + c[19] * (3 * zz);
+  r[4] += c[11] * y + c[12] * z + c[10] * x * 3; r[4] += r[4];
+  r[5] += c[11] * x * 2 + c[13] * y * 2 + c[14] * z;
+  r[6] += c[12] * x * 2 + c[15] * z * 2 + c[14] * y;
+  r[7] += c[13] * x + c[17] * z + c[16] * y * 3; r[7] += r[7];
+  r[8] += c[14] * x + c[17] * y * 2 + c[18] * z * 2;
+  r[9] += c[15] * x + c[18] * y + c[19] * z * 3; r[9] += r[9];
+  r[10] *= 6; r[11] += r[11]; r[12] += r[12]; r[13] += r[13]; r[15] += r[15];
+  r[16] *= 6; r[17] += r[17]; r[18] += r[18]; r[19] *= 6;
+}
+typedef struct {
+  double center[3];
+  double s[MAXM][MAXM];   /* OrthoNormal::coeff(), lower triangular (basis/linear.hpp, integrator/function.hpp:138-172) */
+} modal_basis_t;
+static void cell_center(const oracle_t *o, int64_t c, double *ctr) { /* image of the local origin */
+  /* mean of the 8 corner nodes = trilinear map at (0,0,0); the corners are nodes (i,j,k) in {0,q-1}^3 */
+  int q = o->q, n = o->n, fq = q * q;
+  for (int k = 0; k < 3; ++k) ctr[k] = 0;
+  for (int a = 0; a < n; ++a) {
+    int i = a / fq, j = (a / q) % q, kk = a % q;
+    if ((i != 0 && i != q - 1) || (j != 0 && j != q - 1) || (kk != 0 && kk != q - 1)) continue;
+    for (int k = 0; k < 3; ++k) ctr[k] += o->xyz[(c * n + a) * 3 + k] / 8;
+  }
+}
+static double global_weight(const oracle_t *o, int64_t c, int a) { /* integrator/hexahedron.hpp: local weight x det */
+  int q = o->q, fq = q * q;
+  return o->w[a / fq] * o->w[(a / q) % q] * o->w[a % q] * o->det[c * o->n + a];
+}
+static void modal_basis_build(const oracle_t *o, int64_t c, modal_basis_t *b) {
+  int n = o->n, m = taylor_count(o->degree);
+  double A[MAXM][MAXM] = {{0}}, S[MAXM][MAXM] = {{0}};
+  cell_center(o, c, b->center);
+  for (int a = 0; a < n; ++a) {
+    double d[3], t[MAXM], w = global_weight(o, c, a);
+    for (int k = 0; k < 3; ++k) d[k] = o->xyz[(c * n + a) * 3 + k] - b->center[k];
+    taylor_values(o->degree, d, t);
+    for (int i = 0; i < m; ++i) for (int j = 0; j < m; ++j) A[i][j] += t[i] * t[j] * w;
+  }
+  for (int i = 0; i < m; ++i) S[i][i] = 1;
+  S[0][0] = 1 / sqrt(A[0][0]);
+  for (int i = 1; i < m; ++i) {
+    for (int j = 0; j < i; ++j) {
+      double temp = 0;
+      for (int k = 0; k <= j; ++k) temp += S[j][k] * A[k][i];
+      for (int l = 0; l <= j; ++l) S[i][l] -= temp * S[j][l];
+    }
+    double norm_sq = 0;
+    for (int j = 0; j <= i; ++j) {
+      double sum = 0, sij = S[i][j];
+      for (int k = 0; k < j; ++k) sum += 2 * S[i][k] * A[k][j];
+      norm_sq += sij * (sij * A[j][j] + sum);
+    }
+    double nrm = sqrt(norm_sq);
+    for (int j = 0; j < m; ++j) S[i][j] /= nrm;
+  }
+  memcpy(b->s, S, sizeof S);
+}
+static void modal_basis_values(const oracle_t *o, const modal_basis_t *b, const double *x, double *phi) {
+  int m = taylor_count(o->degree);
+  double d[3] = {x[0] - b->center[0], x[1] - b->center[1], x[2] - b->center[2]}, t[MAXM];
+  taylor_values(o->degree, d, t);
+  for (int i = 0; i < m; ++i) {
+    double v = 0;
+    for (int j = 0; j <= i; ++j) v += b->s[i][j] * t[j];
+    phi[i] = v;
+  }
+}
+/* weno::GetSmoothness (limiter/weno.hpp:78-95, 37-75) of one component given on my orthonormal basis */
+static double weno_smoothness(const oracle_t *o, int64_t c, const modal_basis_t *b, const double *coef) {
+  int n = o->n, m = taylor_count(o->degree);
+  double tc[MAXM], integral[MAXM] = {0};
+  for (int j = 0; j < m; ++j) { /* GetCoeffOnTaylorBasis = coeff * basis.coeff() */
+    double v = 0;
+    for (int i = j; i < m; ++i) v += coef[i] * b->s[i][j];
+    tc[j] = v;
+  }
+  for (int a = 0; a < n; ++a) {
+    double d[3], pdv[MAXM], w = global_weight(o, c, a);
+    for (int k = 0; k < 3; ++k) d[k] = o->xyz[(c * n + a) * 3 + k] - b->center[k];
+    taylor_partial_derivatives(o->degree, d, tc, pdv);
+    for (int i = 0; i < m; ++i) integral[i] += pdv[i] * pdv[i] * w;
+  }
+  double volume = 1 / (b->s[0][0] * b->s[0][0]);
+  double total = (integral[1] + integral[2] + integral[3]) * (pow(volume, 1 * 2. / 3 - 1) / (tgamma(2) * tgamma(2)));
+  static const int begin[4] = {1, 4, 10, 20};
+  for (int p = 2; p <= o->degree; ++p) {
+    double sm = 0;
+    for (int i = begin[p - 1]; i < begin[p]; ++i) sm += integral[i];
+    total += sm * (pow(volume, p * 2. / 3 - 1) / (tgamma(p + 1) * tgamma(p + 1)));
+  }
+  return total;
+}
+/* limiter::Reconstruct(part, weno::Lazy(w0, eps)) on a single part: every cell is an inner cell, one Jacobi
+   sweep (limiter/reconstruct.hpp:21-54, limiter/weno.hpp:97-195, polynomial/extrapolation.hpp:60-90) */
+void oracle_weno_lazy(void *h, double w0, double eps, double *u) {
+  oracle_t *o = h;
+  int n = o->n, m = taylor_count(o->degree);
+  int64_t nc = o->n_cells;
+  modal_basis_t *basis = malloc(sizeof(modal_basis_t) * nc);
+  double *modal = malloc(sizeof(double) * nc * 5 * m), *fresh = malloc(sizeof(double) * nc * 5 * m);
+  for (int64_t c = 0; c < nc; ++c) { /* Extrapolation::UpdateModalCoeff */
+    modal_basis_build(o, c, &basis[c]);
+    double *mc = &modal[c * 5 * m];
+    memset(mc, 0, sizeof(double) * 5 * m);
+    for (int a = 0; a < n; ++a) {
+      double phi[MAXM], w = global_weight(o, c, a);
+      modal_basis_values(o, &basis[c], &o->xyz[(c * n + a) * 3], phi);
+      for (int k = 0; k < 5; ++k) for (int i = 0; i < m; ++i) mc[k * m + i] += u[(c * n + a) * 5 + k] * (phi[i] * w);
+    }
+  }
+  /* adjacency in face order */
+  int *adj_cnt = calloc(nc, sizeof(int));
+  int64_t *adj = malloc(sizeof(int64_t) * nc * 6);
+  for (int64_t f = 0; f < o->n_interior; ++f) {
+    int64_t a = o->holder[f], b = o->sharer[f];
+    adj[a * 6 + adj_cnt[a]++] = b;
+    adj[b * 6 + adj_cnt[b]++] = a;
+  }
+  for (int64_t c = 0; c < nc; ++c) {
+    const modal_basis_t *mb = &basis[c];
+    const double *mine = &modal[c * 5 * m];
+    int cnt = adj_cnt[c];
+    double cand[7][5][MAXM];
+    double s00 = mb->s[0][0];
+    for (int j = 0; j < cnt; ++j) { /* Borrow: project the neighbour's modal polynomial onto my basis */
+      int64_t d = adj[c * 6 + j];
+      memset(cand[j], 0, sizeof cand[j]);
+      for (int a = 0; a < n; ++a) {
+        double phi[MAXM], phn[MAXM], w = global_weight(o, c, a);
+        const double *x = &o->xyz[(c * n + a) * 3];
+        modal_basis_values(o, mb, x, phi);
+        modal_basis_values(o, &basis[d], x, phn);
+        for (int k = 0; k < 5; ++k) {
+          double v = 0;
+          for (int i = 0; i < m; ++i) v += modal[(d * 5 + k) * m + i] * phn[i];
+          for (int i = 0; i < m; ++i) cand[j][k][i] += v * phi[i] * w;
+        }
+      }
+      for (int k = 0; k < 5; ++k) /* adj_proj += my_average - adj_proj.average() (projection.hpp:257-261) */
+        cand[j][k][0] += (mine[k * m] * s00 - cand[j][k][0] * s00) / s00;
+    }
+    for (int k = 0; k < 5; ++k) for (int i = 0; i < m; ++i) cand[cnt][k][i] = mine[k * m + i];
+    for (int k = 0; k < 5; ++k) {
+      double wgt[7], sum = 0;
+      for (int j = 0; j <= cnt; ++j) {
+        double beta = weno_smoothness(o, c, mb, cand[j][k]) + eps;
+        double w = j < cnt ? w0 : w0 * (-cnt) + 1.0;
+        wgt[j] = w / (beta * beta);
+        sum += wgt[j];
+      }
+      for (int j = 0; j <= cnt; ++j) wgt[j] /= sum;
+      for (int i = 0; i < m; ++i) {
+        double v = cand[cnt][k][i] * wgt[cnt];
+        for (int j = 0; j < cnt; ++j) v += cand[j][k][i] * wgt[j];
+        fresh[(c * 5 + k) * m + i] = v;
+      }
+    }
+  }
+  for (int64_t c = 0; c < nc; ++c) /* Extrapolation::SetCoeff(modal) -> UpdateNodalCoeff */
+    for (int a = 0; a < n; ++a) {
+      double phi[MAXM];
+      modal_basis_values(o, &basis[c], &o->xyz[(c * n + a) * 3], phi);
+      for (int k = 0; k < 5; ++k) {
+        double v = 0;
+        for (int i = 0; i < m; ++i) v += fresh[(c * 5 + k) * m + i] * phi[i];
+        u[(c * n + a) * 5 + k] = v;
+      }
+    }
+  free(basis); free(modal); free(fresh); free(adj_cnt); free(adj);
+}
+
 /* one rotated Riemann problem (test hook) */
 void oracle_riemann_flux(int riemann, int bc_kind, const double *frame9, const double *ul, const double *ur,
     double *f) {

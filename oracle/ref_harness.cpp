@@ -50,6 +50,10 @@
 // including it (demo/euler/sourceless.hpp:11), and so do we.
 using Scalar = double;
 #include "mini/limiter/majority.hpp"
+#include "mini/limiter/reconstruct.hpp"
+#include "mini/limiter/weno.hpp"
+#include "mini/polynomial/extrapolation.hpp"
+#include "mini/spatial/with_limiter.hpp"
 #include "mini/polynomial/hexahedron.hpp"
 #include "mini/riemann/euler/ausm.hpp"
 #include "mini/riemann/euler/exact.hpp"
@@ -467,6 +471,11 @@ using Value = typename Poly::Value;
 using Global = typename Poly::Global;
 using BcFunc = std::function<Value(const Global &, double)>;
 using Column = typename mini::temporal::System<Scalar>::Column;
+// nodal expansion with its modal (orthonormal) extension, as demo/euler/sourceless.hpp:41-43 composes it under LIMITER
+using ModalPoly = mini::polynomial::Extrapolation<Poly>;
+using ModalPart = OraclePart<ModalPoly>;
+// (w0, eps) of the next weno limiter to be created (demo/euler/sourceless.cpp:114); set by ref_pN_set_weno
+static double g_weno_w0 = 0.001, g_weno_eps = 1e-6;
 
 extern "C" typedef void (*ref_value_callback)(int tag, const double *xyz, double t, double *out,
     void *user);
@@ -537,6 +546,7 @@ struct SolverBase {
   virtual void set_bc(int tag, int kind, FieldSpec const &spec) = 0;
   virtual void approximate(FieldSpec const &spec) = 0;
   virtual void set_solution(int r, const double *col) = 0;
+  virtual void set_solution_all(const double *cols) = 0;
   virtual void get_solution(int r, double *col) const = 0;
   virtual void residual_all(double t) = 0;
   virtual void get_residual(int r, double *col) const = 0;
@@ -546,10 +556,18 @@ struct SolverBase {
   virtual void limiter(int kind) = 0;
 };
 
+struct NoLimiter { NoLimiter(double, double) {} };
+template <class Cell, bool kModal> struct LimiterOf { using type = NoLimiter; };
+template <class Cell> struct LimiterOf<Cell, true> { using type = mini::limiter::weno::Lazy<Cell>; };
+
 template <class Spatial>
 struct SolverImpl : SolverBase {
+  using Part = typename Spatial::Part;   // OraclePart<Poly>, or OraclePart<Extrapolation<Poly>> under a limiter
+  static constexpr bool kLimited = mini::polynomial::Modal<typename Part::Polynomial>;
+  using Limiter = typename LimiterOf<typename Part::Cell, kLimited>::type;
   GlobalMesh mesh;
   std::unique_ptr<InProcessComm> comm;
+  std::vector<std::unique_ptr<Limiter>> limiters;   // one per part: the limiter object is stateful
   std::vector<std::unique_ptr<Part>> parts;
   std::vector<std::unique_ptr<Spatial>> spatials;
   std::vector<Column> residuals;
@@ -563,8 +581,12 @@ struct SolverImpl : SolverBase {
     ForEachPart([this](int r) {
       parts[r] = std::make_unique<Part>(&mesh, comm.get(), r);
     });
+    limiters.resize(mesh.n_parts);
     ForEachPart([this, c_next](int r) {
-      if constexpr (std::is_constructible_v<Spatial, Part *, Scalar>) {
+      if constexpr (kLimited) {   // demo/euler/sourceless.cpp:114-120: Spatial(&limiter, &part)
+        limiters[r] = std::make_unique<Limiter>(g_weno_w0, g_weno_eps);
+        spatials[r] = std::make_unique<Spatial>(limiters[r].get(), parts[r].get());
+      } else if constexpr (std::is_constructible_v<Spatial, Part *, Scalar>) {
         spatials[r] = std::make_unique<Spatial>(parts[r].get(), c_next);   // fr::General(part, c_next)
       } else {
         spatials[r] = std::make_unique<Spatial>(parts[r].get());
@@ -668,10 +690,22 @@ struct SolverImpl : SolverBase {
     return dt;
   }
   void limiter(int kind) override {
-    for (auto &p : parts) {
-      if (kind == 0) mini::limiter::average::Reconstruct(p.get());
-      else mini::limiter::majority::Reconstruct(p.get());
+    if constexpr (!kLimited) {
+      for (auto &p : parts) {
+        if (kind == 0) mini::limiter::average::Reconstruct(p.get());
+        else mini::limiter::majority::Reconstruct(p.get());
+      }
     }
+  }
+  // all parts at once: under a limiter SetSolutionColumn exchanges ghost cells (with_limiter.hpp:58-61,
+  // limiter/reconstruct.hpp:47-51), which needs every part to take part
+  void set_solution_all(const double *cols) override {
+    std::vector<const double *> begin(mesh.n_parts);
+    for (int r = 0; r < mesh.n_parts; ++r) { begin[r] = cols; cols += parts[r]->GetCellDataSize(); }
+    ForEachPart([&](int r) {
+      Column c = Eigen::Map<const Column>(begin[r], parts[r]->GetCellDataSize());
+      spatials[r]->SetSolutionColumn(c);
+    });
   }
   void cell_geometry(int r, double *length, double *volume) const override {
     for (auto &c : parts[r]->local_cells_) {
@@ -717,6 +751,12 @@ static SolverBase *Create(int scheme, int riemann, GlobalMesh &&mesh) {
     case 0: return new SolverImpl<sp::fr::General<Part, RExact>>(std::move(mesh), g_c_next);
     case 1: return new SolverImpl<sp::fr::General<Part, RHllc>>(std::move(mesh), g_c_next);
     case 2: return new SolverImpl<sp::fr::General<Part, RAusm>>(std::move(mesh), g_c_next);
+    }
+  } else if (scheme == 4) {   // WithLimiter<fr::Lobatto, weno::Lazy> (demo/euler/sourceless.hpp:72-80 with FR + LIMITER)
+    using Lazy = mini::limiter::weno::Lazy<typename ModalPart::Cell>;
+    switch (riemann) {
+    case 0: return new SolverImpl<sp::WithLimiter<sp::fr::Lobatto<ModalPart, RExact>, Lazy>>(std::move(mesh));
+    case 1: return new SolverImpl<sp::WithLimiter<sp::fr::Lobatto<ModalPart, RHllc>, Lazy>>(std::move(mesh));
     }
   } else if (scheme == 3) {
     switch (riemann) {
@@ -807,6 +847,8 @@ void REF_FN(approximate)(void *h, int field_kind, const double *params, int n_pa
   s.user = user;
   static_cast<SolverBase *>(h)->approximate(s);
 }
+void REF_FN(set_weno)(double w0, double eps) { oracle::g_weno_w0 = w0; oracle::g_weno_eps = eps; }
+void REF_FN(set_solution_all)(void *h, const double *cols) { static_cast<SolverBase *>(h)->set_solution_all(cols); }
 void REF_FN(set_solution)(void *h, int r, const double *col) {
   static_cast<SolverBase *>(h)->set_solution(r, col);
 }

@@ -87,6 +87,11 @@ class Oracle:
         lib().oracle_limiter(self.h, C.c_int(kind), _dp(u))
         return u
 
+    def weno_lazy(self, u, w0=0.001, eps=1e-6):
+        u = np.array(u, dtype=np.float64, copy=True)
+        lib().oracle_weno_lazy(self.h, C.c_double(w0), C.c_double(eps), _dp(u))
+        return u
+
     def time_step(self, u, dt_guess, rk_order):
         u = np.ascontiguousarray(u, dtype=np.float64)
         return float(lib().oracle_time_step(self.h, _dp(u), C.c_double(dt_guess), C.c_int(rk_order)))

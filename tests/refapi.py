@@ -12,7 +12,7 @@ _libs: dict[int, C.CDLL] = {}
 
 CB = C.CFUNCTYPE(None, C.c_int, C.POINTER(C.c_double), C.c_double, C.POINTER(C.c_double), C.c_void_p)
 
-FR, DG, FR_GENERAL, FR_VISCOUS = 0, 1, 2, 3
+FR, DG, FR_GENERAL, FR_VISCOUS, FR_WENO_LAZY = 0, 1, 2, 3, 4
 EXACT, HLLC, AUSM = 0, 1, 2
 # boundary kinds, order of fem.hpp:196-222 as used by ref_harness.cpp
 WALL, SUPERSONIC_OUTLET, SUPERSONIC_INLET, SUBSONIC_INLET, SUBSONIC_OUTLET, SMART, NO_SLIP = range(7)
@@ -41,7 +41,8 @@ def _i32(a):
 
 
 class Ref:
-    def __init__(self, mesh, degree=2, scheme=FR, riemann=HLLC, cell_parts=None, n_parts=1, c_next=0.0):
+    def __init__(self, mesh, degree=2, scheme=FR, riemann=HLLC, cell_parts=None, n_parts=1, c_next=0.0,
+                 weno=(0.001, 1e-6)):
         if degree not in _libs:
             _libs[degree] = C.CDLL(lib_path(degree))
         self.lib = _libs[degree]
@@ -50,6 +51,7 @@ class Ref:
         self.n_nodes_per_cell = (degree + 1) ** 3
         self.kfields = 5 * self.n_nodes_per_cell
         self._f("set_vincent")(C.c_double(c_next))
+        self._f("set_weno")(C.c_double(weno[0]), C.c_double(weno[1]))
         f = self._f("create")
         f.restype = C.c_void_p
         nodes = np.ascontiguousarray(mesh.nodes, dtype=np.float64)
@@ -130,6 +132,14 @@ class Ref:
         col = np.ascontiguousarray(col, dtype=np.float64)
         assert col.size == self.count_local(r) * self.kfields
         self._f("set_solution")(self.h, C.c_int(r), _dp(col))
+
+    def set_solution_all(self, cols):
+        """Every part's column at once (list, or one concatenated array): under a limiter the reference's
+        SetSolutionColumn exchanges ghost cells, so all parts must take part."""
+        col = np.ascontiguousarray(np.concatenate([np.asarray(c, dtype=np.float64).reshape(-1) for c in cols])
+                                   if isinstance(cols, (list, tuple)) else cols, dtype=np.float64)
+        assert col.size == sum(self.count_local(r) for r in range(self.n_parts)) * self.kfields
+        self._f("set_solution_all")(self.h, _dp(col))
 
     def get_solution(self, r=0):
         out = np.empty(self.count_local(r) * self.kfields)
