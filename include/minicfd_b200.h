@@ -229,6 +229,19 @@ int mcfd_limiter_reconstruct(mcfd_ctx *ctx, int kind);
 /* -- diagnostics --------------------------------------------------------------------------------- */
 
 /* Number of kernels this context has launched so far (bench.py's gpu_launches). */
+/* Replaces mini::limiter::Reconstruct(part, &limiter) with limiter = mini::limiter::weno::Lazy<Cell>(w0, eps)
+ * (include/mini/limiter/reconstruct.hpp:21-54, include/mini/limiter/weno.hpp:97-195) on cells whose polynomial is
+ * mini::polynomial::Extrapolation<Hexahedron> (include/mini/polynomial/extrapolation.hpp:20-188): the nodal
+ * values are projected on the cell's orthonormal basis (include/mini/basis/linear.hpp:87-141,
+ * include/mini/polynomial/projection.hpp:28-51), every neighbour's polynomial is re-projected on that basis and
+ * shifted to the cell's mean, the candidates are blended with weights w / (beta + eps)^2 from the Taylor-derivative
+ * smoothness indicators (weno.hpp:25-95), and the nodal values are re-sampled from the blend.  Acts on the state the
+ * next residual would read (the current solution, or the newest stage inside an open RK step) — the reference's
+ * WithLimiter does the same after every SetSolutionColumn (include/mini/spatial/with_limiter.hpp:57-68).
+ * phase 0 = inner cells (they need no ghost data), phase 1 = inter cells (call after mcfd_halo_unpack of the
+ * UNLIMITED state, exactly like reconstruct.hpp:46-51; they borrow the already limited inner cells), -1 = both. */
+int mcfd_limiter_weno_lazy(mcfd_ctx *ctx, double w0, double eps, int phase);
+
 int64_t mcfd_launch_count(const mcfd_ctx *ctx);
 /* Duration in ms of the stage kernels launched since the last call with reset != 0, measured with
  * CUDA events on the context's stream when timing is enabled (bench.py's roofline leg). */

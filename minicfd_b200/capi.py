@@ -72,6 +72,7 @@ SYMBOLS = {
     "mcfd_rk_step_device": (C.c_int, [_P, C.c_int, C.c_double, _P]),
     "mcfd_time_step_static": (C.c_int, [C.c_int32, C.c_int32, C.c_int64, _P, _P, C.c_double, C.c_int32, _P, _P]),
     "mcfd_limiter_reconstruct": (C.c_int, [_P, C.c_int]),
+    "mcfd_limiter_weno_lazy": (C.c_int, [_P, C.c_double, C.c_double, C.c_int]),
     "mcfd_launch_count": (C.c_int64, [_P]),
     "mcfd_enable_kernel_timing": (C.c_int, [_P, C.c_int]),
     "mcfd_kernel_time": (C.c_int, [_P, _D, _I64, C.c_int]),
@@ -132,6 +133,9 @@ class Context:
         self.kfields = 5 * self.q ** 3
         self.n_local = 0
         self._cb = None
+
+    def limiter_weno_lazy(self, w0, eps, phase=-1):
+        self._check(self.lib.mcfd_limiter_weno_lazy(self.h, w0, eps, phase))
 
     def set_diffusion(self, beta_0, beta_1, nu, prandtl):
         self._check(self.lib.mcfd_set_diffusion(self.h, beta_0, beta_1, nu, prandtl))

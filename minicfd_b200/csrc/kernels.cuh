@@ -761,6 +761,275 @@ void RunStageBlockOnHost(const StageArgs &p, int bid, double *smem) {
 }
 #endif
 
+// ---- WENO limiter on the modal extension of the nodal expansion -----------------
+// mini::polynomial::Extrapolation<Hexahedron> keeps, next to the nodal values, their L2 projection on a
+// per-cell orthonormal basis phi = S * taylor(x - center) (polynomial/extrapolation.hpp:60-90,
+// basis/linear.hpp:87-141, integrator/function.hpp:138-172); weno::Lazy (limiter/weno.hpp:97-195) blends
+// that projection with the neighbours' polynomials re-projected on the cell's own basis, weighted by
+// Taylor-derivative smoothness indicators (weno.hpp:25-95), and the nodal values are re-sampled from the
+// blend.  Per cell the host stores BAS = centre (3), S packed row-wise (M(M+1)/2), the smoothness weights
+// volume^(2k/3-1)/(k!)^2 for k = 1..3; the device works per (cell, component) because the components never
+// mix in weno::Lazy.  All sums over quadrature points use moments against the *Taylor* monomials:
+//     g_k = sum_q W_q taylor_k(x_q - c) f(x_q),     projection on phi:  a = S g,    Taylor form:  t = S^T a.
+template <int P>
+struct ModalShape {
+  static constexpr int M = (P == 2) ? 10 : 20;            // basis/taylor.hpp:27-31
+  static constexpr int kTri = M * (M + 1) / 2;
+  static constexpr int kBasRows = 3 + kTri + 3;
+  static constexpr int kSOffset = 3, kWOffset = 3 + kTri;
+};
+
+template <int P>
+MCFD_HD void TaylorValues(const double *d, double *t) {   // basis/taylor.hpp:204-218
+  const double x = d[0], y = d[1], z = d[2];
+  t[0] = 1; t[1] = x; t[2] = y; t[3] = z;
+  t[4] = x * x; t[5] = x * y; t[6] = x * z; t[7] = y * y; t[8] = y * z; t[9] = z * z;
+  if (P == 3) {
+    t[10] = x * t[4]; t[11] = x * t[5]; t[12] = x * t[6]; t[13] = x * t[7]; t[14] = x * t[8]; t[15] = x * t[9];
+    t[16] = y * t[7]; t[17] = y * t[8]; t[18] = y * t[9]; t[19] = z * t[9];
+  }
+}
+
+// Sum of the squared partial derivatives of each order at one point (Taylor::GetPartialDerivatives,
+// basis/taylor.hpp:241-372, squared and grouped as weno.hpp:55-75 groups them): sq[k-1] for order k.
+template <int P>
+MCFD_HD void TaylorDerivativeSquares(const double *d, const double *c, double *sq) {
+  const double x = d[0], y = d[1], z = d[2];
+  double r1 = c[1] + c[4] * (2 * x) + c[5] * y + c[6] * z;
+  double r2 = c[2] + c[5] * x + c[7] * (2 * y) + c[8] * z;
+  double r3 = c[3] + c[6] * x + c[8] * y + c[9] * (2 * z);
+  double r4 = c[4], r5 = c[5], r6 = c[6], r7 = c[7], r8 = c[8], r9 = c[9];
+  if (P == 3) {
+    const double xx = x * x, xy = x * y, xz = x * z, yy = y * y, yz = y * z, zz = z * z;
+    r1 += c[10] * (3 * xx) + c[11] * (2 * xy) + c[12] * (2 * xz) + c[13] * yy + c[14] * yz + c[15] * zz;
+    r2 += c[11] * xx + c[14] * xz + c[13] * (2 * xy) + c[16] * (3 * yy) + c[17] * (2 * yz) + c[18] * zz;
+    r3 += c[12] * xx + c[14] * xy + c[15] * (2 * xz) + c[17] * yy + c[18] * (2 * yz) + c[19] * (3 * zz);
+    r4 += c[11] * y + c[12] * z + c[10] * x * 3;
+    r5 += c[11] * x * 2 + c[13] * y * 2 + c[14] * z;
+    r6 += c[12] * x * 2 + c[15] * z * 2 + c[14] * y;
+    r7 += c[13] * x + c[17] * z + c[16] * y * 3;
+    r8 += c[14] * x + c[17] * y * 2 + c[18] * z * 2;
+    r9 += c[15] * x + c[18] * y + c[19] * z * 3;
+  }
+  r4 += r4; r7 += r7; r9 += r9;
+  sq[0] = r1 * r1 + r2 * r2 + r3 * r3;
+  sq[1] = r4 * r4 + r5 * r5 + r6 * r6 + r7 * r7 + r8 * r8 + r9 * r9;
+  if (P == 3) {
+    const double a = c[10] * 6, b = c[11] * 2, e = c[12] * 2, f = c[13] * 2, g = c[14], h = c[15] * 2;
+    const double i = c[16] * 6, j = c[17] * 2, k = c[18] * 2, l = c[19] * 6;
+    sq[2] = a * a + b * b + e * e + f * f + g * g + h * h + i * i + j * j + k * k + l * l;
+  }
+}
+
+// offset of quadrature point n from the cell centre, and its global weight (local weight x det J)
+template <int Q>
+MCFD_HD void QuadraturePoint(int n, const double *geo, int gs, double *d, double *w) {
+  constexpr int FQ = Q * Q;
+  const int i = n / FQ, j = (n / Q) % Q, k = n % Q;
+  const double x = c_tab.xi[i], e = c_tab.xi[j], z = c_tab.xi[k];
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    d[a] = geo[(0 + a) * gs] * x + geo[(3 + a) * gs] * e + geo[(6 + a) * gs] * z + geo[(9 + a) * gs] * (x * e)
+         + geo[(12 + a) * gs] * (e * z) + geo[(15 + a) * gs] * (z * x) + geo[(18 + a) * gs] * (x * e * z);
+  }
+  const Metric m = ComputeMetric(geo, gs, x, e, z);
+  *w = c_tab.w[i] * c_tab.w[j] * c_tab.w[k] * m.det;
+}
+
+// a = S g (orthonormal coefficients from Taylor moments) and t = S^T a (Taylor coefficients);
+// S packed row-wise, rows `ss` doubles apart
+template <int M>
+MCFD_HD void MomentsToModal(const double *S, int ss, const double *g, double *a) {
+  int r = 0;
+  for (int i = 0; i < M; ++i) {
+    double v = 0;
+    for (int j = 0; j <= i; ++j) v = fma(S[(size_t)(r + j) * ss], g[j], v);
+    a[i] = v;
+    r += i + 1;
+  }
+}
+template <int M>
+MCFD_HD void ModalToTaylor(const double *S, int ss, const double *a, double *t) {
+  for (int j = 0; j < M; ++j) t[j] = 0;
+  int r = 0;
+  for (int i = 0; i < M; ++i) {
+    for (int j = 0; j <= i; ++j) t[j] = fma(a[i], S[(size_t)(r + j) * ss], t[j]);
+    r += i + 1;
+  }
+}
+
+// Extrapolation::UpdateModalCoeff for one (cell, component): u rows `us` apart (node-major, component
+// already selected), quadrature table quad[n*4 + {dx,dy,dz,W}] rows `qs` apart, outputs rows `os` apart.
+template <int Q>
+MCFD_HD void ModalProjectCell(const double *u, int us, const double *quad, int qs, const double *bas, int bs,
+    double *mod, double *tay, int os) {
+  constexpr int P = Q - 1, N = Q * Q * Q, M = ModalShape<P>::M;
+  double g[M], a[M], t[M];
+  for (int k = 0; k < M; ++k) g[k] = 0;
+  for (int n = 0; n < N; ++n) {
+    const double d[3] = {quad[(size_t)(n * 4) * qs], quad[(size_t)(n * 4 + 1) * qs], quad[(size_t)(n * 4 + 2) * qs]};
+    const double wf = quad[(size_t)(n * 4 + 3) * qs] * u[(size_t)(n * 5) * us];
+    double tv[M];
+    TaylorValues<P>(d, tv);
+    for (int k = 0; k < M; ++k) g[k] = fma(tv[k], wf, g[k]);
+  }
+  const double *S = bas + (size_t)ModalShape<P>::kSOffset * bs;
+  MomentsToModal<M>(S, bs, g, a);
+  ModalToTaylor<M>(S, bs, a, t);
+  for (int k = 0; k < M; ++k) { mod[(size_t)k * os] = a[k]; tay[(size_t)k * os] = t[k]; }
+}
+
+// weno::GetSmoothness of one component given on my orthonormal basis (limiter/weno.hpp:78-95, 37-75)
+template <int Q>
+MCFD_HD double WenoSmoothness(const double *a, const double *quad, int qs, const double *bas, int bs) {
+  constexpr int P = Q - 1, N = Q * Q * Q, M = ModalShape<P>::M;
+  double t[M], sum[3] = {0, 0, 0};
+  ModalToTaylor<M>(bas + (size_t)ModalShape<P>::kSOffset * bs, bs, a, t);
+  for (int n = 0; n < N; ++n) {
+    const double d[3] = {quad[(size_t)(n * 4) * qs], quad[(size_t)(n * 4 + 1) * qs], quad[(size_t)(n * 4 + 2) * qs]};
+    const double w = quad[(size_t)(n * 4 + 3) * qs];
+    double sq[3];
+    TaylorDerivativeSquares<P>(d, t, sq);
+    for (int k = 0; k < P; ++k) sum[k] = fma(sq[k], w, sum[k]);
+  }
+  double beta = 0;
+  for (int k = 0; k < P; ++k) beta += sum[k] * bas[(size_t)(ModalShape<P>::kWOffset + k) * bs];
+  return beta;
+}
+
+struct WenoArgs {
+  double *u;              // state tiles (nodal values); cells of the batch are overwritten
+  const double *geom, *bas, *h2s;
+  const int *nbr;
+  const unsigned char *code;
+  double *mod, *tay;      // [tile][comp*M + k][lane] orthonormal / Taylor coefficients of every cell
+  double *mod_new, *tay_new;  // the limited cells' new coefficients (copied over after the batch)
+  int cell_begin, cell_end;
+  double w0, eps;
+};
+
+// weno::Lazy::Reconstruct for one (cell, component) (limiter/weno.hpp:127-194) + Extrapolation::SetCoeff
+// (polynomial/extrapolation.hpp:119-122, 66-71).  `tile`, `tl`: my cell; quad/bas as above.
+template <int Q>
+MCFD_HD void WenoLazyCell(const WenoArgs &p, int tile, int tl, int comp, const double *quad, int qs,
+    const double *bas, int bs) {
+  constexpr int P = Q - 1, N = Q * Q * Q, F = 5 * N, M = ModalShape<P>::M;
+  const double *S = bas + (size_t)ModalShape<P>::kSOffset * bs;
+  const double s00 = S[0];
+  double mine[M], fresh[M];
+  const double *my_mod = p.mod + ((size_t)tile * 5 * M + comp * M) * kTile + tl;
+  for (int k = 0; k < M; ++k) { mine[k] = my_mod[(size_t)k * kTile]; fresh[k] = 0; }
+  const double my_average = mine[0] * s00;                  // projection.hpp:46-51
+  int adj_cnt = 0;
+  double sum_w = 0;
+  for (int f = 0; f < 6; ++f) {
+    const int nb = p.nbr[((size_t)tile * 6 + f) * kTile + tl];
+    if (nb < 0) continue;
+    ++adj_cnt;
+    // my centre -> neighbour's centre: +-HolderToSharer (through the face, so periodic pairs work too)
+    const bool holder = (p.code[((size_t)tile * 6 + f) * kTile + tl] & 64) != 0;
+    const double *hv = p.h2s + ((size_t)tile * 18 + f * 3) * kTile + tl;
+    const double sg = holder ? 1.0 : -1.0;
+    const double off[3] = {sg * hv[0], sg * hv[kTile], sg * hv[2 * kTile]};
+    const double *nt = p.tay + ((size_t)(nb >> 5) * 5 * M + comp * M) * kTile + (nb & 31);
+    double tb[M], g[M], cand[M];
+    for (int k = 0; k < M; ++k) { tb[k] = nt[(size_t)k * kTile]; g[k] = 0; }
+    for (int n = 0; n < N; ++n) {   // Borrow: neighbour's polynomial at my quadrature points, projected on my basis
+      const double d[3] = {quad[(size_t)(n * 4) * qs], quad[(size_t)(n * 4 + 1) * qs], quad[(size_t)(n * 4 + 2) * qs]};
+      const double dn[3] = {d[0] - off[0], d[1] - off[1], d[2] - off[2]};
+      double tv[M];
+      TaylorValues<P>(dn, tv);
+      double v = 0;
+      for (int k = 0; k < M; ++k) v = fma(tb[k], tv[k], v);
+      v *= quad[(size_t)(n * 4 + 3) * qs];
+      TaylorValues<P>(d, tv);
+      for (int k = 0; k < M; ++k) g[k] = fma(tv[k], v, g[k]);
+    }
+    MomentsToModal<M>(S, bs, g, cand);
+    cand[0] += (my_average - cand[0] * s00) / s00;           // projection.hpp:257-261
+    double beta = WenoSmoothness<Q>(cand, quad, qs, bas, bs) + p.eps;
+    const double w = p.w0 / (beta * beta);
+    sum_w += w;
+    for (int k = 0; k < M; ++k) fresh[k] = fma(w, cand[k], fresh[k]);
+  }
+  {
+    double beta = WenoSmoothness<Q>(mine, quad, qs, bas, bs) + p.eps;
+    const double w = (p.w0 * (-adj_cnt) + 1.0) / (beta * beta);
+    sum_w += w;
+    for (int k = 0; k < M; ++k) fresh[k] = fma(w, mine[k], fresh[k]);
+  }
+  const double inv = 1.0 / sum_w;
+  for (int k = 0; k < M; ++k) fresh[k] *= inv;
+  double t[M];
+  ModalToTaylor<M>(S, bs, fresh, t);
+  double *new_mod = p.mod_new + ((size_t)tile * 5 * M + comp * M) * kTile + tl;
+  double *new_tay = p.tay_new + ((size_t)tile * 5 * M + comp * M) * kTile + tl;
+  for (int k = 0; k < M; ++k) { new_mod[(size_t)k * kTile] = fresh[k]; new_tay[(size_t)k * kTile] = t[k]; }
+  double *dst = p.u + (size_t)tile * F * kTile + tl;
+  for (int n = 0; n < N; ++n) {   // UpdateNodalCoeff: the blend sampled at my nodes
+    const double d[3] = {quad[(size_t)(n * 4) * qs], quad[(size_t)(n * 4 + 1) * qs], quad[(size_t)(n * 4 + 2) * qs]};
+    double tv[M];
+    TaylorValues<P>(d, tv);
+    double v = 0;
+    for (int k = 0; k < M; ++k) v = fma(t[k], tv[k], v);
+    dst[(size_t)(n * 5 + comp) * kTile] = v;
+  }
+}
+
+#ifdef __CUDACC__
+// One CTA per tile, five warps: warp = component, lanes = cells.  Quadrature offsets/weights and the
+// cell's basis are staged in shared memory by all warps first.
+template <int Q>
+struct WenoShape {
+  static constexpr int P = Q - 1, N = Q * Q * Q;
+  static constexpr size_t kSharedBytes = (size_t)(N * 4 + ModalShape<P>::kBasRows) * kTile * sizeof(double);
+};
+template <int Q>
+__device__ __forceinline__ void WenoStage(const double *geom, const double *bas, int tile, double *sQuad, double *sBas) {
+  constexpr int N = Q * Q * Q, kBasRows = ModalShape<Q - 1>::kBasRows;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int n = warp; n < N; n += 5) {
+    double d[3], w;
+    QuadraturePoint<Q>(n, geom + (size_t)tile * kGeomRows * kTile + lane, kTile, d, &w);
+    sQuad[(n * 4 + 0) * kTile + lane] = d[0]; sQuad[(n * 4 + 1) * kTile + lane] = d[1];
+    sQuad[(n * 4 + 2) * kTile + lane] = d[2]; sQuad[(n * 4 + 3) * kTile + lane] = w;
+  }
+  for (int i = threadIdx.x; i < kBasRows * kTile; i += 160) sBas[i] = bas[(size_t)tile * kBasRows * kTile + i];
+  __syncthreads();
+}
+template <int Q>
+__global__ void __launch_bounds__(160) ModalKernel(const double *u, const double *geom, const double *bas,
+    double *mod, double *tay, int tile_begin, int cell_begin, int cell_end) {
+  constexpr int P = Q - 1, N = Q * Q * Q, F = 5 * N, M = ModalShape<P>::M;
+  extern __shared__ double smem[];
+  double *sQuad = smem, *sBas = smem + N * 4 * kTile;
+  const int tile = tile_begin + blockIdx.x, lane = threadIdx.x & 31, comp = threadIdx.x >> 5;
+  WenoStage<Q>(geom, bas, tile, sQuad, sBas);
+  const int cell = tile * kTile + lane;
+  if (cell < cell_begin || cell >= cell_end) return;
+  ModalProjectCell<Q>(u + (size_t)tile * F * kTile + comp * kTile + lane, kTile, sQuad + lane, kTile, sBas + lane, kTile,
+      mod + ((size_t)tile * 5 * M + comp * M) * kTile + lane, tay + ((size_t)tile * 5 * M + comp * M) * kTile + lane, kTile);
+}
+template <int Q>
+__global__ void __launch_bounds__(160) WenoLazyKernel(WenoArgs p, int tile_begin) {
+  constexpr int N = Q * Q * Q;
+  extern __shared__ double smem[];
+  double *sQuad = smem, *sBas = smem + N * 4 * kTile;
+  const int tile = tile_begin + blockIdx.x, lane = threadIdx.x & 31, comp = threadIdx.x >> 5;
+  WenoStage<Q>(p.geom, p.bas, tile, sQuad, sBas);
+  const int cell = tile * kTile + lane;
+  if (cell < p.cell_begin || cell >= p.cell_end) return;
+  WenoLazyCell<Q>(p, tile, lane, comp, sQuad + lane, kTile, sBas + lane, kTile);
+}
+// new coefficients of the cells of a finished batch -> the tables the next batch borrows from
+__global__ void CopyCellRowsKernel(const double *src, double *dst, int rows, int cell_begin, int cell_end) {
+  const int cell = cell_begin + blockIdx.x * blockDim.x + threadIdx.x;
+  if (cell >= cell_end) return;
+  const size_t base = (size_t)(cell >> 5) * rows * kTile + (cell & 31);
+  for (int r = 0; r < rows; ++r) dst[base + (size_t)r * kTile] = src[base + (size_t)r * kTile];
+}
+#endif
+
 // Traces of cells [cell_begin, cell_end) (local and ghost alike): one CTA per tile, the tile's state and
 // geometry staged in shared memory, lanes = cells, nodes dealt to the warps.
 template <int Q>

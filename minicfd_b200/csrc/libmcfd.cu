@@ -52,6 +52,8 @@ struct mcfd_ctx {
   std::map<int32_t, int32_t> tag_kind;
   DevBuf<double> u[3], res, geom, bvals, length, column;
   DevBuf<double> grad, hn, h2s;                 // viscous traces (TraceKernel) and HolderToSharer vectors
+  DevBuf<double> bas, mod, tay, mod_new, tay_new;   // WENO limiter: per-cell bases and modal coefficients
+  int64_t first_inter = 0;                      // local cells [first_inter, n_local) have a ghost neighbour
   Viscosity vis{2.0, 1.0 / 12, 0.0, 0.0};       // Direct::SetBetaValues / NavierStokes::SetProperty
   double prandtl = 0.708;
   DevBuf<int> nbr, send_cells, recv_cells;
@@ -349,10 +351,13 @@ int mcfd_set_mesh(mcfd_ctx *ctx, int64_t n_nodes, const double *xyz, int64_t n_l
     MCFD_CUDA(ctx, cudaMemset(b.p, 0, state * sizeof(double)));
   }
   ctx->res.Free();
-  if (ctx->cfg.diffusion != MCFD_INVISCID) {
+  {
     auto h2s = ToTiles(ctx->mesh.h2s, 18, ctx->n_cells, ctx->n_tiles);
     MCFD_CUDA(ctx, ctx->h2s.Alloc(h2s.size()));
     MCFD_CUDA(ctx, cudaMemcpy(ctx->h2s.p, h2s.data(), h2s.size() * sizeof(double), cudaMemcpyHostToDevice));
+  }
+  ctx->bas.Free();
+  if (ctx->cfg.diffusion != MCFD_INVISCID) {
     MCFD_CUDA(ctx, ctx->grad.Alloc((size_t)ctx->n_tiles * ctx->n_nodes * 15 * kTile));
     MCFD_CUDA(ctx, ctx->hn.Alloc((size_t)ctx->n_tiles * 6 * ctx->q * ctx->q * 15 * kTile));
     MCFD_CUDA(ctx, cudaMemset(ctx->grad.p, 0, ctx->grad.n * sizeof(double)));
@@ -376,6 +381,7 @@ int mcfd_set_mesh(mcfd_ctx *ctx, int64_t n_nodes, const double *xyz, int64_t n_l
   for (int64_t c = 0; c < n_local && first_inter == n_local; ++c)
     for (int f = 0; f < 6; ++f)
       if (ctx->mesh.nbr[c * 6 + f] >= n_local) { first_inter = c; break; }
+  ctx->first_inter = first_inter;
   ctx->total_blocks = (n_local + ctx->cpb - 1) / ctx->cpb;
   // without ghosts the whole part goes in one launch; with ghosts only full blocks of inner cells
   ctx->inner_blocks = (n_ghost == 0) ? ctx->total_blocks : first_inter / ctx->cpb;
@@ -708,6 +714,79 @@ int mcfd_limiter_reconstruct(mcfd_ctx *ctx, int kind) {
   else CellConstantKernel<4><<<blocks, threads, 0, ctx->stream>>>(ctx->u[ctx->cur].p, ctx->geom.p, n, kind);
   MCFD_CUDA(ctx, cudaGetLastError());
   ctx->launches++;
+  return MCFD_OK;
+}
+
+}  // extern "C"
+
+namespace {
+
+template <int Q>
+int WenoLazyBatch(mcfd_ctx *ctx, double *u, double w0, double eps, int64_t modal_begin, int64_t modal_end,
+    int64_t cell_begin, int64_t cell_end, bool publish) {
+  constexpr int M = ModalShape<Q - 1>::M;
+  const size_t smem = WenoShape<Q>::kSharedBytes;
+  static bool configured = false;
+  if (!configured) {
+    MCFD_CUDA(ctx, cudaFuncSetAttribute(ModalKernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    MCFD_CUDA(ctx, cudaFuncSetAttribute(WenoLazyKernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = true;
+  }
+  if (modal_end > modal_begin) {   // Extrapolation::UpdateModalCoeff of the cells whose nodal values are new
+    const int t0 = (int)(modal_begin / kTile), t1 = (int)((modal_end + kTile - 1) / kTile);
+    ModalKernel<Q><<<t1 - t0, 160, smem, ctx->stream>>>(u, ctx->geom.p, ctx->bas.p, ctx->mod.p, ctx->tay.p, t0,
+        (int)modal_begin, (int)modal_end);
+    ctx->launches++;
+  }
+  if (cell_end > cell_begin) {
+    WenoArgs a;
+    a.u = u; a.geom = ctx->geom.p; a.bas = ctx->bas.p; a.h2s = ctx->h2s.p; a.nbr = ctx->nbr.p; a.code = ctx->code.p;
+    a.mod = ctx->mod.p; a.tay = ctx->tay.p; a.mod_new = ctx->mod_new.p; a.tay_new = ctx->tay_new.p;
+    a.cell_begin = (int)cell_begin; a.cell_end = (int)cell_end; a.w0 = w0; a.eps = eps;
+    const int t0 = (int)(cell_begin / kTile), t1 = (int)((cell_end + kTile - 1) / kTile);
+    WenoLazyKernel<Q><<<t1 - t0, 160, smem, ctx->stream>>>(a, t0);
+    ctx->launches++;
+    if (publish) {   // the next batch borrows the limited polynomials of this one (limiter/reconstruct.hpp:41-51)
+      const int n = (int)(cell_end - cell_begin), threads = 128, blocks = (n + threads - 1) / threads;
+      CopyCellRowsKernel<<<blocks, threads, 0, ctx->stream>>>(ctx->tay_new.p, ctx->tay.p, 5 * M, (int)cell_begin, (int)cell_end);
+      CopyCellRowsKernel<<<blocks, threads, 0, ctx->stream>>>(ctx->mod_new.p, ctx->mod.p, 5 * M, (int)cell_begin, (int)cell_end);
+      ctx->launches += 2;
+    }
+  }
+  MCFD_CUDA(ctx, cudaGetLastError());
+  return MCFD_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int mcfd_limiter_weno_lazy(mcfd_ctx *ctx, double w0, double eps, int phase) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (phase < -1 || phase > 1) return Fail(ctx, MCFD_ERR_ARG, "phase must be -1 (both), 0 (inner cells) or 1 (inter cells)");
+  const int m = ctx->q == 3 ? 10 : 20, rows = ctx->q == 3 ? ModalShape<2>::kBasRows : ModalShape<3>::kBasRows;
+  if (!ctx->bas.p) {   // first use: per-cell orthonormal bases, built on the host like the reference does at set-up
+    auto bas = ToTiles(ctx->mesh.BuildModalBases(ctx->cfg.degree), rows, ctx->n_cells, ctx->n_tiles);
+    MCFD_CUDA(ctx, ctx->bas.Alloc(bas.size()));
+    MCFD_CUDA(ctx, cudaMemcpy(ctx->bas.p, bas.data(), bas.size() * sizeof(double), cudaMemcpyHostToDevice));
+    const size_t n = (size_t)ctx->n_tiles * 5 * m * kTile;
+    for (DevBuf<double> *b : {&ctx->mod, &ctx->tay, &ctx->mod_new, &ctx->tay_new}) {
+      MCFD_CUDA(ctx, b->Alloc(n));
+      MCFD_CUDA(ctx, cudaMemset(b->p, 0, n * sizeof(double)));
+    }
+  }
+  double *u = HaloState(ctx);
+  const int64_t nl = ctx->mesh.n_local, nc = ctx->n_cells, fi = ctx->mesh.n_ghost ? ctx->first_inter : nl;
+  auto batch = [&](int64_t mb, int64_t me, int64_t cb, int64_t ce, bool publish) {
+    return ctx->q == 3 ? WenoLazyBatch<3>(ctx, u, w0, eps, mb, me, cb, ce, publish)
+                       : WenoLazyBatch<4>(ctx, u, w0, eps, mb, me, cb, ce, publish);
+  };
+  if (phase != 1) {   // act(inner cells): needs no ghost cell (limiter/reconstruct.hpp:46-48)
+    if (int s = batch(0, nl, 0, fi, fi < nl)) return s;
+  }
+  if (phase != 0) {   // act(inter cells) after UpdateGhostCellCoeffs (limiter/reconstruct.hpp:49-51)
+    if (int s = batch(nl, nc, fi, nl, false)) return s;
+  }
   return MCFD_OK;
 }
 

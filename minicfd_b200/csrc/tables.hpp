@@ -267,6 +267,73 @@ struct HostMesh {
     }
   }
 
+  // Per-cell orthonormal basis of the modal extension (basis::OrthoNormal, basis/linear.hpp:87-141):
+  // Gram-Schmidt on the Taylor monomials about the cell centre with the cell's own quadrature
+  // (integrator/function.hpp:138-172).  Row layout per cell: ModalShape<P> in kernels.cuh.
+  std::vector<double> BuildModalBases(int degree) const {
+    const int q = degree + 1, m = degree == 2 ? 10 : 20, tri = m * (m + 1) / 2, rows = 3 + tri + 3;
+    const int64_t nc = n_local + n_ghost;
+    double x[kMaxQ], w[kMaxQ];
+    LobattoRule(q, x, w);
+    std::vector<double> bas((size_t)nc * rows, 0.0);
+    std::vector<double> A(m * m), S(m * m);
+    for (int64_t c = 0; c < nc; ++c) {
+      const double *g = &coef[c * kGeomRows];
+      std::fill(A.begin(), A.end(), 0.0);
+      for (int i = 0; i < q; ++i) for (int j = 0; j < q; ++j) for (int k = 0; k < q; ++k) {
+        const double xi = x[i], et = x[j], ze = x[k];
+        double d[3], r[3][3];
+        for (int a = 0; a < 3; ++a) {
+          d[a] = g[0 + a] * xi + g[3 + a] * et + g[6 + a] * ze + g[9 + a] * (xi * et) + g[12 + a] * (et * ze)
+               + g[15 + a] * (ze * xi) + g[18 + a] * (xi * et * ze);
+          r[0][a] = g[0 + a] + g[9 + a] * et + g[15 + a] * ze + g[18 + a] * et * ze;
+          r[1][a] = g[3 + a] + g[9 + a] * xi + g[12 + a] * ze + g[18 + a] * xi * ze;
+          r[2][a] = g[6 + a] + g[12 + a] * et + g[15 + a] * xi + g[18 + a] * xi * et;
+        }
+        const double det = r[0][0] * (r[1][1] * r[2][2] - r[1][2] * r[2][1])
+                         - r[0][1] * (r[1][0] * r[2][2] - r[1][2] * r[2][0])
+                         + r[0][2] * (r[1][0] * r[2][1] - r[1][1] * r[2][0]);
+        const double wq = w[i] * w[j] * w[k] * det;
+        double t[20];
+        t[0] = 1; t[1] = d[0]; t[2] = d[1]; t[3] = d[2];
+        t[4] = d[0] * d[0]; t[5] = d[0] * d[1]; t[6] = d[0] * d[2]; t[7] = d[1] * d[1]; t[8] = d[1] * d[2]; t[9] = d[2] * d[2];
+        if (m == 20) {
+          t[10] = d[0] * t[4]; t[11] = d[0] * t[5]; t[12] = d[0] * t[6]; t[13] = d[0] * t[7]; t[14] = d[0] * t[8];
+          t[15] = d[0] * t[9]; t[16] = d[1] * t[7]; t[17] = d[1] * t[8]; t[18] = d[1] * t[9]; t[19] = d[2] * t[9];
+        }
+        for (int a = 0; a < m; ++a) for (int b = 0; b < m; ++b) A[a * m + b] += t[a] * t[b] * wq;
+      }
+      std::fill(S.begin(), S.end(), 0.0);
+      for (int i = 0; i < m; ++i) S[i * m + i] = 1;
+      S[0] = 1 / std::sqrt(A[0]);
+      for (int i = 1; i < m; ++i) {
+        for (int j = 0; j < i; ++j) {
+          double temp = 0;
+          for (int k = 0; k <= j; ++k) temp += S[j * m + k] * A[k * m + i];
+          for (int l = 0; l <= j; ++l) S[i * m + l] -= temp * S[j * m + l];
+        }
+        double norm_sq = 0;
+        for (int j = 0; j <= i; ++j) {
+          double sum = 0, sij = S[i * m + j];
+          for (int k = 0; k < j; ++k) sum += 2 * S[i * m + k] * A[k * m + j];
+          norm_sq += sij * (sij * A[j * m + j] + sum);
+        }
+        const double nrm = std::sqrt(norm_sq);
+        for (int j = 0; j < m; ++j) S[i * m + j] /= nrm;
+      }
+      double *out = &bas[(size_t)c * rows];
+      for (int a = 0; a < 3; ++a) out[a] = c0[c * 3 + a];
+      int r = 3;
+      for (int i = 0; i < m; ++i) for (int j = 0; j <= i; ++j) out[r++] = S[i * m + j];
+      const double volume = 1 / (S[0] * S[0]);                      // OrthoNormal::Measure, basis/linear.hpp:127-130
+      for (int k = 1; k <= 3; ++k) {                                // Smoothness::GetWeight, limiter/weno.hpp:50-53
+        const double kf = std::tgamma(k + 1.0);
+        out[r++] = std::pow(volume, k * 2. / 3 - 1) / (kf * kf);
+      }
+    }
+    return bas;
+  }
+
   bool Build(int degree, int64_t n_nodes, const double *xyz, int64_t nl, int64_t ng,
       const int64_t *cn, int64_t n_bfaces, const int64_t *bf, const int32_t *btag,
       int64_t n_pairs, const int64_t *pairs) {

@@ -31,6 +31,7 @@ class Spatial:
         self.comm = comm            # halo exchanger (minicfd_b200.halo) or None for a single part
         if comm is not None:
             comm.attach(self)
+        self._limiter = None        # (w0, eps) of the weno::Lazy limiter, or None
         self._bc_funcs = {}         # tag -> (kind, func or None, time_dependent)
         self._bc_points = {}
         self._t = 0.0
@@ -73,6 +74,27 @@ class Spatial:
         demo/laminar/cavity.cpp:30-38; ignored by inviscid systems (fr/general.hpp:455-459)."""
         self._set_bc(tag, capi.BC_NO_SLIP_WALL, func, time_dependent)
 
+    def SetLimiter(self, w0=0.001, eps=1e-6):
+        """Makes this object behave like `WithLimiter<General, limiter::weno::Lazy<Cell>>(&limiter, &part)` with
+        `limiter(w0, eps)` (spatial/with_limiter.hpp:21-68, demo/euler/sourceless.cpp:114-120): the limiter runs
+        after every SetSolutionColumn / Approximate and after every Runge-Kutta stage.  None switches it off."""
+        self._limiter = None if w0 is None else (float(w0), float(eps))
+
+    def Reconstruct(self):
+        """mini::limiter::Reconstruct(part, limiter) (limiter/reconstruct.hpp:21-54): ShareGhostCellCoeffs, limit
+        the inner cells, UpdateGhostCellCoeffs, limit the inter cells."""
+        if self._limiter is None:
+            return
+        w0, eps = self._limiter
+        if self.comm is None:
+            self.ctx.limiter_weno_lazy(w0, eps, -1)
+            return
+        self.comm.drain()
+        self.comm.start()                      # the unlimited values travel
+        self.ctx.limiter_weno_lazy(w0, eps, 0)
+        self.comm.finish()
+        self.ctx.limiter_weno_lazy(w0, eps, 1)
+
     def SetDiffusion(self, beta_0, beta_1, nu, prandtl):
         """Riemann::Diffusion::SetBetaValues + SetProperty (direct.hpp:80-83, navier_stokes.hpp:57-60)."""
         self.ctx.set_diffusion(beta_0, beta_1, nu, prandtl)
@@ -99,6 +121,7 @@ class Spatial:
         if self.comm is not None:
             self.comm.drain()              # an exchange of the old state may still be in flight
         self.ctx.set_solution(column)
+        self.Reconstruct()                 # with_limiter.hpp:57-61
 
     def GetSolutionColumn(self):
         return self.ctx.get_solution()
@@ -145,11 +168,27 @@ class RungeKutta:
 
     def Update(self, system: Spatial, t, dt):
         ctx = system.ctx
+        if system._limiter is not None:
+            ctx.rk_begin(self.order, t, dt)
+            self._stages_with_limiter(system)
+            return
         if system.comm is None:
             ctx.rk_step(self.order, t, dt)
             return
         ctx.rk_begin(self.order, t, dt)
         self._stages_with_halo(system)
+
+    def _stages_with_limiter(self, system: Spatial):
+        """rk.hpp:16-49 on a WithLimiter system: every SetSolutionColumn of a stage result is followed by the
+        limiter (with_limiter.hpp:57-61), whose own ghost exchange carries the unlimited values; the next
+        residual exchanges the limited ones (fem.hpp:249-256)."""
+        ctx, comm = system.ctx, system.comm
+        for stage in range(self.order):
+            if comm is not None:
+                comm.exchange()
+            ctx.rk_stage_inner(stage)
+            ctx.rk_stage_inter(stage)
+            system.Reconstruct()
 
     def _stages_with_halo(self, system: Spatial):
         """Every stage: the inner cells advance on the main stream (fem.hpp:249-254) while a high-priority

@@ -395,6 +395,8 @@ typedef struct {
   double d2[MAXQ][MAXQ];               /* d2[i][m] = l_m''(x_i) */
   double *jtgrad;   /* [cell][n][3][3][3] d(J^-T)/d(xi_a) = mat_after_grad_of_U_, hexahedron.hpp:233-236 */
   double *dist;     /* [face][q*q] normal . HolderToSharer, fem.hpp:83-85 */
+  int limited;      /* WithLimiter<.., weno::Lazy>(w0, eps): the limiter follows every SetSolutionColumn */
+  double weno_w0, weno_eps;
   double c_next;                       /* fr::General only (fr/general.hpp:218-219) */
   int64_t n_cells;
   double x[MAXQ], w[MAXQ], d1[MAXQ][MAXQ]; /* d1[i][m] = l_m'(x_i) */
@@ -935,7 +937,13 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
   free(fhat);
 }
 
-/* temporal/rk.hpp:16-49 with temporal/ode.hpp:121-133, on whole columns */
+void oracle_weno_lazy(void *h, double w0, double eps, double *u);
+void oracle_set_limiter(void *h, int on, double w0, double eps) {
+  oracle_t *o = h;
+  o->limited = on; o->weno_w0 = w0; o->weno_eps = eps;
+}
+/* temporal/rk.hpp:16-49 with temporal/ode.hpp:121-133, on whole columns; SET() = System::SetSolutionColumn, which
+   under WithLimiter is followed by the limiter (spatial/with_limiter.hpp:57-61) */
 void oracle_rk_update(void *h, int order, double t, double dt, double *u) {
   oracle_t *o = h;
   int64_t m = o->n_cells * o->n * 5;
@@ -943,19 +951,24 @@ void oracle_rk_update(void *h, int order, double t, double dt, double *u) {
   memcpy(u0, u, sizeof(double) * m);
 #define EULER_NEXT(tt, dst) do { oracle_residual(o, (tt), u, r); \
     for (int64_t i = 0; i < m; ++i) { r[i] *= dt; dst[i] = u[i] + r[i]; } } while (0)
+#define LIMIT() do { if (o->limited) oracle_weno_lazy(o, o->weno_w0, o->weno_eps, u); } while (0)
   if (order == 1) {
-    EULER_NEXT(t, un); memcpy(u, un, sizeof(double) * m);
+    EULER_NEXT(t, un); memcpy(u, un, sizeof(double) * m); LIMIT();
   } else if (order == 2) {
-    EULER_NEXT(t, un); memcpy(u, un, sizeof(double) * m);
+    EULER_NEXT(t, un); memcpy(u, un, sizeof(double) * m); LIMIT();
     EULER_NEXT(t + dt, un);
     for (int64_t i = 0; i < m; ++i) { un[i] += u0[i]; un[i] *= 0.5; u[i] = un[i]; }
+    LIMIT();
   } else {
-    EULER_NEXT(t, un); memcpy(u, un, sizeof(double) * m);
+    EULER_NEXT(t, un); memcpy(u, un, sizeof(double) * m); LIMIT();
     EULER_NEXT(t + dt, un);
     for (int64_t i = 0; i < m; ++i) { double v = u0[i] * 3; v += un[i]; v /= 4; u[i] = v; }
+    LIMIT();
     EULER_NEXT(t + dt / 2, un);
     for (int64_t i = 0; i < m; ++i) { double v = un[i] * 2; v += u0[i]; v /= 3; u[i] = v; }
+    LIMIT();
   }
+#undef LIMIT
 #undef EULER_NEXT
   free(r); free(u0); free(un);
 }

@@ -121,3 +121,8 @@ def apply_viscous_spatial(sp, kinds=VISCOUS_BCS, vis=VISCOUS):
             sp.SetSupersonicInlet(tag, viscous_bc_function(k))
         else:
             sp.SetSmartBoundary(tag, viscous_bc_function(k))
+
+
+# ---- weno::Lazy limiter -------------------------------------------------------------
+WENO = (0.001, 1e-6)                                   # demo/euler/sourceless.cpp:114
+WENO_GOLDEN_CASES = [("weno_p2_hllc", 2, 1), ("weno_p3_hllc", 3, 1)]   # (name, degree, riemann)

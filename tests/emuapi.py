@@ -76,6 +76,28 @@ def stage(mesh, degree, scheme, riemann, column_in, *, n_local=None, n_ghost=0, 
     return out
 
 
+def weno_lazy(mesh, degree, column_in, w0=0.001, eps=1e-6, *, n_local=None, n_ghost=0, cells=None, bfaces=None,
+              btags=None):
+    cells = np.ascontiguousarray(mesh.cells if cells is None else cells, dtype=np.int64)
+    bfaces = np.ascontiguousarray(mesh.bfaces if bfaces is None else bfaces, dtype=np.int64)
+    btags = np.ascontiguousarray(mesh.btags if btags is None else btags, dtype=np.int32)
+    nodes = np.ascontiguousarray(mesh.nodes, dtype=np.float64)
+    if n_local is None:
+        n_local = len(cells)
+    F = 5 * (degree + 1) ** 3
+    column_in = np.ascontiguousarray(column_in, dtype=np.float64)
+    assert column_in.size == (n_local + n_ghost) * F
+    pairs = None if mesh.periodic is None else np.ascontiguousarray(mesh.periodic, dtype=np.int64)
+    out = np.empty(n_local * F)
+    rc = lib().emu_weno_lazy(C.c_int(degree), C.c_int64(len(nodes)), _dp(nodes), C.c_int64(n_local), C.c_int64(n_ghost),
+                             _ip(cells), C.c_int64(len(bfaces)), _ip(bfaces), _i32(btags),
+                             C.c_int64(0 if pairs is None else len(pairs)), _ip(pairs), C.c_double(w0), C.c_double(eps),
+                             _dp(column_in), _dp(out))
+    if rc != 0:
+        raise RuntimeError("emu_weno_lazy failed")
+    return out
+
+
 def riemann(kind, n, ul, ur, bc=-1):
     out = np.empty(5)
     n = np.ascontiguousarray(n, dtype=np.float64)

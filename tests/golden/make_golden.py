@@ -46,6 +46,18 @@ def main():
         np.savez_compressed(os.path.join(HERE, name + ".npz"), u=u, residual=res, dt=dt, u_rk3=u_rk3,
                             nodes=m.nodes, cells=m.cells, bfaces=m.bfaces, btags=m.btags)
         print(name, np.linalg.norm(res), dt)
+    # WithLimiter<fr::Lobatto, weno::Lazy>: the limiter's action on a column, and an RK3 step with it
+    for name, degree, riemann in cases.WENO_GOLDEN_CASES:
+        r = refapi.Ref(m, degree=degree, scheme=refapi.FR_WENO_LAZY, riemann=riemann, weno=cases.WENO)
+        cases.apply_bcs_ref(r)
+        u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), amp=1e-2)
+        r.set_solution_all(u)
+        limited = r.get_solution()
+        r.rk_update(3, 0.0, cases.GOLDEN_DT, 1)
+        u_rk3 = r.get_solution()
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), u=u, limited=limited, u_rk3=u_rk3,
+                            nodes=m.nodes, cells=m.cells, bfaces=m.bfaces, btags=m.btags)
+        print(name, np.abs(limited - u).max())
 
 
 if __name__ == "__main__":

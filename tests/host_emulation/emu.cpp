@@ -101,6 +101,82 @@ int emu_stage(int degree, int scheme, int riemann, int64_t n_nodes, const double
   return 0;
 }
 
+}  // extern "C"
+
+// weno::Lazy limiter on the host: the device functions of kernels.cuh, one (cell, component) at a time, in the
+// same two batches as mcfd_limiter_weno_lazy.  column: [n_cells][F] in, [n_local][F] out.
+template <int Q>
+static void RunWeno(HostMesh const &mesh, std::vector<double> &u, std::vector<double> const &geom,
+    std::vector<int> const &nbr, std::vector<unsigned char> const &code, std::vector<double> const &h2s,
+    std::vector<double> const &bas, int64_t first_inter, double w0, double eps) {
+  constexpr int P = Q - 1, N = Q * Q * Q, F = 5 * N, M = ModalShape<P>::M, R = ModalShape<P>::kBasRows;
+  const int64_t nl = mesh.n_local, nc = mesh.n_local + mesh.n_ghost, nt = (nc + kTile - 1) / kTile;
+  std::vector<double> quad((size_t)nt * N * 4 * kTile, 0.0), mod((size_t)nt * 5 * M * kTile, 0.0), tay(mod), modn(mod), tayn(mod);
+  for (int64_t c = 0; c < nc; ++c) {
+    const int64_t t = c >> 5; const int l = c & 31;
+    for (int n = 0; n < N; ++n) {
+      double d[3], w;
+      QuadraturePoint<Q>(n, geom.data() + t * kGeomRows * kTile + l, kTile, d, &w);
+      for (int a = 0; a < 3; ++a) quad[(t * N * 4 + n * 4 + a) * kTile + l] = d[a];
+      quad[(t * N * 4 + n * 4 + 3) * kTile + l] = w;
+    }
+  }
+  auto modal = [&](int64_t b, int64_t e) {
+    for (int64_t c = b; c < e; ++c) for (int k = 0; k < 5; ++k) {
+      const int64_t t = c >> 5; const int l = c & 31;
+      ModalProjectCell<Q>(u.data() + t * F * kTile + k * kTile + l, kTile, quad.data() + t * N * 4 * kTile + l, kTile,
+          bas.data() + t * R * kTile + l, kTile, mod.data() + (t * 5 * M + k * M) * kTile + l,
+          tay.data() + (t * 5 * M + k * M) * kTile + l, kTile);
+    }
+  };
+  WenoArgs a;
+  a.u = u.data(); a.geom = geom.data(); a.bas = bas.data(); a.h2s = h2s.data(); a.nbr = nbr.data(); a.code = code.data();
+  a.mod = mod.data(); a.tay = tay.data(); a.mod_new = modn.data(); a.tay_new = tayn.data(); a.w0 = w0; a.eps = eps;
+  auto limit = [&](int64_t b, int64_t e) {
+    a.cell_begin = (int)b; a.cell_end = (int)e;
+    for (int64_t c = b; c < e; ++c) for (int k = 0; k < 5; ++k) {
+      const int64_t t = c >> 5; const int l = c & 31;
+      WenoLazyCell<Q>(a, (int)t, l, k, quad.data() + t * N * 4 * kTile + l, kTile, bas.data() + t * R * kTile + l, kTile);
+    }
+    for (int64_t c = b; c < e; ++c) for (int r = 0; r < 5 * M; ++r) {
+      const size_t i = ((c >> 5) * 5 * M + r) * kTile + (c & 31);
+      tay[i] = tayn[i]; mod[i] = modn[i];
+    }
+  };
+  const int64_t fi = mesh.n_ghost ? first_inter : nl;
+  modal(0, nl); limit(0, fi);
+  modal(nl, nc); limit(fi, nl);
+}
+
+extern "C" {
+
+int emu_weno_lazy(int degree, int64_t n_nodes, const double *xyz, int64_t n_local, int64_t n_ghost,
+    const int64_t *cell_nodes, int64_t n_bfaces, const int64_t *bface_nodes, const int32_t *bface_tags,
+    int64_t n_pairs, const int64_t *pairs, double w0, double eps, const double *column_in, double *column_out) {
+  const int q = degree + 1, F = 5 * q * q * q;
+  c_tab = BuildTables(degree, 0, (q == 3) ? kP2Warps : kP3Warps, kTile / ((q == 3) ? kP2Cells : kP3Cells));
+  HostMesh mesh;
+  if (!mesh.Build(degree, n_nodes, xyz, n_local, n_ghost, cell_nodes, n_bfaces, bface_nodes, bface_tags, n_pairs, pairs))
+    return -1;
+  const int64_t nc = n_local + n_ghost, nt = (nc + kTile - 1) / kTile;
+  auto geom = ToTiles(mesh.coef, kGeomRows, nc, nt);
+  auto nbr = ToTiles(mesh.nbr, 6, nc, nt);
+  auto code = ToTiles(mesh.code, 6, nc, nt);
+  auto h2s = ToTiles(mesh.h2s, 18, nc, nt);
+  auto bas = ToTiles(mesh.BuildModalBases(degree), q == 3 ? ModalShape<2>::kBasRows : ModalShape<3>::kBasRows, nc, nt);
+  std::vector<double> u((size_t)nt * F * kTile, 0.0);
+  for (int64_t c = 0; c < nc; ++c)
+    for (int f = 0; f < F; ++f) u[((c >> 5) * F + f) * kTile + (c & 31)] = column_in[c * F + f];
+  int64_t first_inter = n_local;
+  for (int64_t c = 0; c < n_local && first_inter == n_local; ++c)
+    for (int f = 0; f < 6; ++f) if (mesh.nbr[c * 6 + f] >= n_local) { first_inter = c; break; }
+  if (q == 3) RunWeno<3>(mesh, u, geom, nbr, code, h2s, bas, first_inter, w0, eps);
+  else RunWeno<4>(mesh, u, geom, nbr, code, h2s, bas, first_inter, w0, eps);
+  for (int64_t c = 0; c < n_local; ++c)
+    for (int f = 0; f < F; ++f) column_out[c * F + f] = u[((c >> 5) * F + f) * kTile + (c & 31)];
+  return 0;
+}
+
 // Boundary-face order and flux-point coordinates as the library defines them.
 int64_t emu_boundary(int degree, int64_t n_nodes, const double *xyz, int64_t n_local, int64_t n_ghost,
     const int64_t *cell_nodes, int64_t n_bfaces, const int64_t *bface_nodes, const int32_t *bface_tags,

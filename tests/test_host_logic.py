@@ -129,6 +129,32 @@ def test_viscous_kernel_source_on_host_matches_golden(name, degree, riemann):
     assert relerr(u3, g["u_rk3"]) < 1e-12
 
 
+@pytest.mark.parametrize("name,degree,riemann", cases.WENO_GOLDEN_CASES)
+def test_weno_kernel_source_on_host_matches_golden(name, degree, riemann):
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    m = meshmod.HexMesh(nodes=g["nodes"], cells=g["cells"], bfaces=g["bfaces"], btags=g["btags"])
+    assert relerr(emuapi.weno_lazy(m, degree, g["u"], *cases.WENO), g["limited"]) < 1e-12
+
+
+@pytest.mark.skipif(not refapi.available(2), reason="oracle/_ref not built (needs /root/reference)")
+def test_weno_two_batches_match_the_reference_parts():
+    """Inner cells first, then inter cells borrowing the already limited inner cells and the UNLIMITED ghost
+    values (limiter/reconstruct.hpp:46-51): the result depends on the partition, and must match part by part."""
+    m = meshmod.scramble(meshmod.box(6, 4, 2, warp=0.1, seed=2), seed=3)
+    parts = (np.arange(m.n_cells) * 2 // m.n_cells).astype(np.int32)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, 2), amp=1e-2)
+    r = refapi.Ref(m, degree=2, scheme=refapi.FR_WENO_LAZY, riemann=1, cell_parts=parts, n_parts=2)
+    P = [Part(m, parts, k, 2) for k in range(2)]
+    r.set_solution_all([p.gather_from_global(u, 135) for p in P])
+    for k, p in enumerate(P):
+        col = u.reshape(-1, 135)[p.global_ids].reshape(-1)
+        class Sub:
+            nodes, periodic = m.nodes, None
+        got = emuapi.weno_lazy(Sub, 2, col, n_local=p.n_local, n_ghost=p.n_ghost, cells=p.cell_nodes,
+                               bfaces=p.bfaces, btags=p.btags)
+        assert relerr(got, r.get_solution(k)) < 1e-12
+
+
 def test_kernel_source_periodic_equals_embedded_box():
     """A periodic box must give the same residuals as the interior of a larger box fed with the same
     2*pi-periodic field (GPU-only periodic variant of BASELINE config 2)."""

@@ -95,6 +95,32 @@ def test_c_oracle_viscous_matches_reference(degree, riemann, nu):
         assert np.array_equal(o0.residual(u, 0.1), o3.residual(u, 0.1))
 
 
+@pytest.mark.parametrize("name,degree,riemann", cases.WENO_GOLDEN_CASES)
+def test_c_oracle_weno_lazy_matches_golden(name, degree, riemann):
+    """weno::Lazy on Extrapolation<Hexahedron> (SURVEY rows a25, a26): the limiter alone and inside RK3."""
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    o = oc.Oracle(_golden_mesh(g), degree, 0, riemann)
+    cases.apply_bcs_oracle(o)
+    limited = o.weno_lazy(g["u"], *cases.WENO)
+    assert relerr(limited, g["limited"]) < TOL
+    assert np.abs(g["limited"] - g["u"]).max() > 1e-3     # the limiter did act
+    o.set_limiter(*cases.WENO)
+    assert relerr(o.rk_update(limited, 3, 0.0, cases.GOLDEN_DT), g["u_rk3"]) < TOL
+
+
+@pytest.mark.skipif(not refapi.available(2), reason="oracle/_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("degree", [2, 3])
+def test_c_oracle_weno_lazy_matches_reference(degree):
+    m = meshmod.scramble(meshmod.box(4, 3, 3, warp=0.2, seed=4), seed=9)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), seed=3, amp=1e-2)
+    r = refapi.Ref(m, degree=degree, scheme=refapi.FR_WENO_LAZY, riemann=1, weno=(0.01, 1e-5))
+    for tag in range(6):
+        r.set_bc(tag, refapi.WALL)
+    r.set_solution_all(u)
+    o = oc.Oracle(m, degree, 0, 1)
+    assert relerr(o.weno_lazy(u, 0.01, 1e-5), r.get_solution()) < TOL
+
+
 def _flux_1d(rho, u, p):
     """Flux of a 1-D primitive state (test/riemann/euler/exact.cpp:34-39)."""
     e = p / 0.4 + 0.5 * rho * u * u
