@@ -50,6 +50,8 @@ def parse():
     ap.add_argument("--cpu-cells", type=int, default=0, help="cells per direction of the CPU sample (0 = auto)")
     ap.add_argument("--viscous", type=float, default=None, metavar="NU",
                     help="run the Navier-Stokes + direct-DG path with this kinematic viscosity (not the headline workload)")
+    ap.add_argument("--limiter", action="store_true",
+                    help="WithLimiter<.., weno::Lazy(0.001, 1e-6)>: the WENO limiter after every stage (not the headline workload)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of replaying a CUDA graph")
@@ -134,6 +136,8 @@ def cpu_run(args, steps, warmup, cells=None):
     scheme = 0 if args.scheme == "fr" else 1
     if args.viscous is not None:
         scheme = 3
+    if args.limiter:
+        scheme = 4
     riemann = RIEMANN[args.riemann]
     kf = 5 * (args.degree + 1) ** 3
     if refapi.available(args.degree):
@@ -158,7 +162,9 @@ def cpu_run(args, steps, warmup, cells=None):
         n_parts = 1
         n = cells or args.cpu_cells or 12
         m = meshmod.box(n, n, n, hi=(10.0, 10.0, 10.0))
-        o = oc.Oracle(m, args.degree, scheme, riemann)
+        o = oc.Oracle(m, args.degree, 0 if args.limiter else scheme, riemann)
+        if args.limiter:
+            o.set_limiter(0.001, 1e-6)
         if args.viscous is not None:
             o.set_viscous(2.0, 1.0 / 12, args.viscous, 0.708)
         for tag in range(6):
@@ -188,6 +194,7 @@ def config_dict(args, n_gpus, dims, part):
                         f"cells total ({args.cells}^3 per GPU), "
                         + ("Euler isentropic vortex, " if args.viscous is None else
                            f"Navier-Stokes (nu={args.viscous}, direct-DG face flux) on the isentropic vortex, ") +
+                        ("weno::Lazy limiter after every stage, " if args.limiter else "") +
                         
                         f"{args.scheme.upper()}-Lobatto p={args.degree}, {args.riemann.upper()}, RK3, periodic",
             "cells_per_gpu": args.cells ** 3, "dof_per_gpu": args.cells ** 3 * 5 * (args.degree + 1) ** 3,
@@ -249,6 +256,8 @@ def ours(args):
                  comm=comm, diffusion=capi.INVISCID if args.viscous is None else capi.NAVIER_STOKES_DDG)
     if args.viscous is not None:
         sp.SetDiffusion(2.0, 1.0 / 12, args.viscous, 0.708)
+    if args.limiter:
+        sp.SetLimiter(0.001, 1e-6)
     sp.ctx.set_stream(torch.cuda.current_stream().cuda_stream)
     sp.Approximate(lambda x: fields.vortex()(x, 0.0))
     if comm is not None:

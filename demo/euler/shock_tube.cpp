@@ -31,13 +31,29 @@ constexpr int kDegrees = 2;
 #include "mini/integrator/lobatto.hpp"
 using Gx = mini::integrator::Lobatto<Scalar, kDegrees + 1>;
 #include "mini/polynomial/hexahedron.hpp"
-using Polynomial = mini::polynomial::Hexahedron<Gx, Gx, Gx, kComponents, false>;
+using Interpolation = mini::polynomial::Hexahedron<Gx, Gx, Gx, kComponents, false>;
+#ifdef LIMITER   // demo/euler/sourceless.hpp:41-47
+#include "mini/polynomial/extrapolation.hpp"
+using Polynomial = mini::polynomial::Extrapolation<Interpolation>;
+#else
+using Polynomial = Interpolation;
+#endif
 #include "mini/mesh/part.hpp"
 using Part = mini::mesh::part::Part<int64_t, Polynomial>;
+using Cell = typename Part::Cell;
 using Global = typename Part::Global;
 using Value = typename Part::Value;
 #include "mini/spatial/fr/lobatto.hpp"
+#ifdef LIMITER   // demo/euler/sourceless.hpp:60-80
+using General = mini::spatial::fr::Lobatto<Part, Riemann>;
+#include "mini/limiter/weno.hpp"
+#include "mini/limiter/reconstruct.hpp"
+#include "mini/spatial/with_limiter.hpp"
+using Limiter = mini::limiter::weno::Lazy<Cell>;
+using Spatial = mini::spatial::WithLimiter<General, Limiter>;
+#else
 using Spatial = mini::spatial::fr::Lobatto<Part, Riemann>;
+#endif
 #include "mini/temporal/rk.hpp"
 constexpr int kOrders = 3;
 using Temporal = mini::temporal::RungeKutta<kOrders, Scalar>;
@@ -78,7 +94,12 @@ int main(int argc, char *argv[]) {
   // input/shock_tube.geo:4-31: [0,5] x [0,0.2] x [0,0.3], h = 0.1
   Part part(0, 1);
   BuildBox(&part, 50, 2, 3, 5.0, 0.2, 0.3);
+#ifdef LIMITER   // demo/euler/sourceless.cpp:114-120
+  auto limiter = Limiter(/* w0 = */0.001, /* eps = */1e-6);
+  Spatial spatial(&limiter, &part);
+#else
   Spatial spatial(&part);
+#endif
   Primitive left, right;
   left.rho() = 1.0; left.u() = 0; left.v() = 0; left.w() = 0; left.p() = 1.0;
   right.rho() = 0.125; right.u() = 0; right.v() = 0; right.w() = 0; right.p() = 0.1;

@@ -86,6 +86,13 @@ struct Hexahedron {  // polynomial/hexahedron.hpp:41-65
   using Local = Global;
   using Value = algebra::Vector<Scalar, K>;
 };
+// polynomial/extrapolation.hpp:20-188: the nodal expansion together with its projection on the cell's orthonormal
+// basis.  On the GPU the modal side exists only inside the limiter kernels, so this is a tag.
+template <class I>
+struct Extrapolation : I {
+  using Interpolation = I;
+  static constexpr bool kModal = true;
+};
 }  // namespace polynomial
 
 namespace riemann {
@@ -214,6 +221,10 @@ class Part {
   static constexpr int kDegrees = Poly::P;
   static constexpr int kComponents = Poly::K;
   static constexpr int kFields = Poly::kFields;
+  struct Cell {   // only what drivers name: `mini::limiter::weno::Lazy<Cell>` (demo/euler/sourceless.hpp:78)
+    using Polynomial = Poly;
+    using Scalar = typename Poly::Scalar;
+  };
 
   struct Halo {
     std::vector<int64_t> parts, send_counts, send_cells, recv_counts, recv_cells;
@@ -487,6 +498,64 @@ class FiniteElementB200 : public temporal::System<typename P::Scalar> {
   mcfd_ctx *ctx_ = nullptr;
   double t_curr_ = 0;
   std::map<int32_t, Bc> bcs_;
+};
+
+}  // namespace spatial
+
+namespace limiter {
+namespace weno {
+// limiter/weno.hpp:97-195; the object only carries (w0, eps), the work is mcfd_limiter_weno_lazy
+template <typename Cell>
+class Lazy {
+ public:
+  using Scalar = typename Cell::Scalar;
+  Lazy(Scalar w0, Scalar eps, bool verbose = false) : w0_(w0), eps_(eps) { (void)verbose; }
+  Scalar w0() const { return w0_; }
+  Scalar eps() const { return eps_; }
+ private:
+  Scalar w0_, eps_;
+};
+}  // namespace weno
+}  // namespace limiter
+
+namespace spatial {
+
+// spatial/with_limiter.hpp:21-68: the limiter follows every SetSolutionColumn / Approximate; a fused RK step
+// runs it after every stage, which is what the column algebra of rk.hpp amounts to on such a system.
+template <typename ConcreteFiniteElement, typename Limiter>
+class WithLimiter : public ConcreteFiniteElement {
+ public:
+  using Base = ConcreteFiniteElement;
+  using Column = typename Base::Column;
+  template <class... Args>
+  WithLimiter(Limiter *limiter_ptr, Args &&...args) : Base(std::forward<Args>(args)...), limiter_ptr_(limiter_ptr) {}
+  Limiter *limiter_ptr() const { return limiter_ptr_; }
+  void SetSolutionColumn(Column const &column) override {
+    this->Base::SetSolutionColumn(column);
+    Reconstruct();
+  }
+  template <class Callable>
+  void Approximate(Callable &&func) {   // Base::Approximate ends in the virtual SetSolutionColumn above
+    Base::Approximate(std::forward<Callable>(func));
+  }
+  bool FusedUpdate(int order, double t_curr, double dt) override {
+    if (this->part().CountGhostCells() > 0) return false;
+    mcfd_ctx *ctx = this->context();
+    b200::Check(mcfd_rk_begin(ctx, order, t_curr, dt), ctx, "mcfd_rk_begin");
+    for (int stage = 0; stage < order; ++stage) {
+      b200::Check(mcfd_rk_stage_inner(ctx, stage), ctx, "mcfd_rk_stage_inner");
+      b200::Check(mcfd_rk_stage_inter(ctx, stage), ctx, "mcfd_rk_stage_inter");
+      Reconstruct();
+    }
+    return true;
+  }
+ private:
+  void Reconstruct() {   // mini::limiter::Reconstruct(part_ptr, limiter_ptr), limiter/reconstruct.hpp:21-54
+    if (!limiter_ptr_) return;
+    mcfd_ctx *ctx = this->context();
+    b200::Check(mcfd_limiter_weno_lazy(ctx, limiter_ptr_->w0(), limiter_ptr_->eps(), -1), ctx, "mcfd_limiter_weno_lazy");
+  }
+  Limiter *limiter_ptr_;
 };
 
 namespace fr {

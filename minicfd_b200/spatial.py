@@ -221,6 +221,10 @@ class RungeKutta:
     def UpdateDevice(self, system: Spatial, t, dt_ptr: int):
         """Update with the time step resident in device memory (no host round trip)."""
         ctx = system.ctx
+        if system._limiter is not None:
+            ctx.rk_begin_device(self.order, t, dt_ptr)
+            self._stages_with_limiter(system)
+            return
         if system.comm is None:
             ctx.rk_step_device(self.order, t, dt_ptr)
             return
