@@ -938,6 +938,7 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
 }
 
 void oracle_weno_lazy(void *h, double w0, double eps, double *u);
+void oracle_weno_eigen(void *h, double w0, double eps, double *u);
 void oracle_set_limiter(void *h, int on, double w0, double eps) {
   oracle_t *o = h;
   o->limited = on; o->weno_w0 = w0; o->weno_eps = eps;
@@ -951,7 +952,8 @@ void oracle_rk_update(void *h, int order, double t, double dt, double *u) {
   memcpy(u0, u, sizeof(double) * m);
 #define EULER_NEXT(tt, dst) do { oracle_residual(o, (tt), u, r); \
     for (int64_t i = 0; i < m; ++i) { r[i] *= dt; dst[i] = u[i] + r[i]; } } while (0)
-#define LIMIT() do { if (o->limited) oracle_weno_lazy(o, o->weno_w0, o->weno_eps, u); } while (0)
+#define LIMIT() do { if (o->limited == 1) oracle_weno_lazy(o, o->weno_w0, o->weno_eps, u); \
+    else if (o->limited == 2) oracle_weno_eigen(o, o->weno_w0, o->weno_eps, u); } while (0)
   if (order == 1) {
     EULER_NEXT(t, un); memcpy(u, un, sizeof(double) * m); LIMIT();
   } else if (order == 2) {
@@ -1222,6 +1224,170 @@ void oracle_weno_lazy(void *h, double w0, double eps, double *u) {
       }
     }
   free(basis); free(modal); free(fresh); free(adj_cnt); free(adj);
+}
+
+/* EigenMatrices (riemann/euler/eigen.hpp:27-56) of a conservative state in the frame (nu, mu, pi) */
+static void eigen_matrices(const double *cons, const frame_t *fr, double L[5][5], double R[5][5]) {
+  prim_t q = cons_to_prim(cons);
+  const double *nu = fr->a, *mu = fr->b, *pi = fr->c;
+  double ux = q.u, uy = q.v, uz = q.w;
+  double u_nu = ux * nu[0] + uy * nu[1] + uz * nu[2];
+  double u_mu = ux * mu[0] + uy * mu[1] + uz * mu[2];
+  double u_pi = ux * pi[0] + uy * pi[1] + uz * pi[2];
+  double a = sound_speed(q.rho, q.p);
+  double ek = (ux * ux + uy * uy + uz * uz) / 2, e0 = a * a * (1 / (GAMMA - 1)), h0 = e0 + ek;
+  double rc[5][5] = { /* columns of R */
+    {1, ux - a * nu[0], uy - a * nu[1], uz - a * nu[2], h0 - a * u_nu},
+    {1, ux, uy, uz, ek},
+    {0, mu[0], mu[1], mu[2], u_mu},
+    {0, pi[0], pi[1], pi[2], u_pi},
+    {1, ux + a * nu[0], uy + a * nu[1], uz + a * nu[2], h0 + a * u_nu}};
+  double b1 = 1 / e0, b2 = b1 * ek;
+  double lc[5][5] = { /* columns of L */
+    {(b2 + u_nu / a) / 2, 1 - b2, -u_mu, -u_pi, (b2 - u_nu / a) / 2},
+    {-(b1 * ux + nu[0] / a) / 2, b1 * ux, mu[0], pi[0], -(b1 * ux - nu[0] / a) / 2},
+    {-(b1 * uy + nu[1] / a) / 2, b1 * uy, mu[1], pi[1], -(b1 * uy - nu[1] / a) / 2},
+    {-(b1 * uz + nu[2] / a) / 2, b1 * uz, mu[2], pi[2], -(b1 * uz - nu[2] / a) / 2},
+    {b1 / 2, -b1, 0, 0, b1 / 2}};
+  for (int i = 0; i < 5; ++i) for (int j = 0; j < 5; ++j) { R[i][j] = rc[j][i]; L[i][j] = lc[j][i]; }
+}
+void oracle_eigen_matrices(const double *cons, const double *frame9, double *L, double *R) {
+  frame_t fr;
+  memcpy(&fr, frame9, sizeof fr);
+  eigen_matrices(cons, &fr, (double (*)[5])L, (double (*)[5])R);
+}
+/* limiter::Reconstruct(part, weno::Eigen(w0, eps)) on a single part (limiter/weno.hpp:197-349): the KXRCF-like
+   detector picks the troubled cells, each of which is rebuilt face by face in characteristic variables */
+void oracle_weno_eigen(void *h, double w0, double eps, double *u) {
+  oracle_t *o = h;
+  int n = o->n, m = taylor_count(o->degree), fq = o->q * o->q;
+  int64_t nc = o->n_cells;
+  modal_basis_t *basis = malloc(sizeof(modal_basis_t) * nc);
+  double *modal = malloc(sizeof(double) * nc * 5 * m), *fresh = malloc(sizeof(double) * nc * 5 * m);
+  double *volume = malloc(sizeof(double) * nc);
+  char *troubled = calloc(nc, 1);
+  for (int64_t c = 0; c < nc; ++c) {
+    modal_basis_build(o, c, &basis[c]);
+    double *mc = &modal[c * 5 * m];
+    memset(mc, 0, sizeof(double) * 5 * m);
+    volume[c] = 0;
+    for (int a = 0; a < n; ++a) {
+      double phi[MAXM], w = global_weight(o, c, a);
+      volume[c] += w;
+      modal_basis_values(o, &basis[c], &o->xyz[(c * n + a) * 3], phi);
+      for (int k = 0; k < 5; ++k) for (int i = 0; i < m; ++i) mc[k * m + i] += u[(c * n + a) * 5 + k] * (phi[i] * w);
+    }
+  }
+  int *adj_cnt = calloc(nc, sizeof(int));
+  int64_t *adj = malloc(sizeof(int64_t) * nc * 6), *adj_face = malloc(sizeof(int64_t) * nc * 6);
+  for (int64_t f = 0; f < o->n_interior; ++f) {
+    int64_t a = o->holder[f], b = o->sharer[f];
+    adj_face[a * 6 + adj_cnt[a]] = f; adj[a * 6 + adj_cnt[a]++] = b;
+    adj_face[b * 6 + adj_cnt[b]] = f; adj[b * 6 + adj_cnt[b]++] = a;
+  }
+  for (int64_t c = 0; c < nc; ++c) { /* Eigen::IsNotSmooth (weno.hpp:230-258) */
+    const modal_basis_t *mb = &basis[c];
+    const int comps[2] = {0, 4};
+    double max_avg[5], sum_diff[5] = {0}, mine[5], phi[MAXM];
+    modal_basis_values(o, mb, mb->center, phi);
+    for (int k = 0; k < 5; ++k) {
+      max_avg[k] = modal[(c * 5 + k) * m] * mb->s[0][0];
+      mine[k] = 0;
+      for (int i = 0; i < m; ++i) mine[k] += modal[(c * 5 + k) * m + i] * phi[i];
+    }
+    for (int t = 0; t < 2; ++t) { int k = comps[t]; max_avg[k] = fmax(1e-9, fabs(max_avg[k])); }
+    for (int j = 0; j < adj_cnt[c]; ++j) {
+      int64_t d = adj[c * 6 + j];
+      double phn[MAXM];
+      modal_basis_values(o, &basis[d], mb->center, phn);
+      for (int t = 0; t < 2; ++t) {
+        int k = comps[t];
+        double v = 0;
+        for (int i = 0; i < m; ++i) v += modal[(d * 5 + k) * m + i] * phn[i];
+        sum_diff[k] += fabs(mine[k] - v);
+        max_avg[k] = fmax(max_avg[k], fabs(modal[(d * 5 + k) * m] * basis[d].s[0][0]));
+      }
+    }
+    double divisor = pow(volume[c], (o->degree + 1.0) / 2.0 / 3) * adj_cnt[c];
+    double reference = o->degree < 3 ? 1.0 : 3.0;
+    for (int t = 0; t < 2; ++t) {
+      int k = comps[t];
+      if (sum_diff[k] / max_avg[k] / divisor > reference) troubled[c] = 1;
+    }
+  }
+  for (int64_t c = 0; c < nc; ++c) {
+    if (!troubled[c]) continue;
+    const modal_basis_t *mb = &basis[c];
+    const double *mine = &modal[c * 5 * m];
+    int cnt = adj_cnt[c];
+    double cand[7][5][MAXM], big_u[5], total[5][MAXM], total_volume = 0;
+    double s00 = mb->s[0][0];
+    for (int j = 0; j < cnt; ++j) { /* Borrow, as in weno::Lazy */
+      int64_t d = adj[c * 6 + j];
+      memset(cand[j], 0, sizeof cand[j]);
+      for (int a = 0; a < n; ++a) {
+        double phi[MAXM], phn[MAXM], w = global_weight(o, c, a);
+        const double *x = &o->xyz[(c * n + a) * 3];
+        modal_basis_values(o, mb, x, phi);
+        modal_basis_values(o, &basis[d], x, phn);
+        for (int k = 0; k < 5; ++k) {
+          double v = 0;
+          for (int i = 0; i < m; ++i) v += modal[(d * 5 + k) * m + i] * phn[i];
+          for (int i = 0; i < m; ++i) cand[j][k][i] += v * phi[i] * w;
+        }
+      }
+      for (int k = 0; k < 5; ++k) cand[j][k][0] += (mine[k * m] * s00 - cand[j][k][0] * s00) / s00;
+    }
+    for (int k = 0; k < 5; ++k) { for (int i = 0; i < m; ++i) cand[cnt][k][i] = mine[k * m + i]; big_u[k] = mine[k * m] * s00; }
+    memset(total, 0, sizeof total);
+    for (int jf = 0; jf < cnt; ++jf) { /* ReconstructOnFace */
+      int64_t f = adj_face[c * 6 + jf];
+      double L[5][5], R[5][5], rot[7][5][MAXM], blend[5][MAXM];
+      eigen_matrices(big_u, &o->frame[f * fq], L, R);
+      for (int j = 0; j <= cnt; ++j)
+        for (int k = 0; k < 5; ++k) for (int i = 0; i < m; ++i) {
+          double v = 0;
+          for (int e = 0; e < 5; ++e) v += L[k][e] * cand[j][e][i];
+          rot[j][k][i] = v;
+        }
+      for (int k = 0; k < 5; ++k) {
+        double wgt[7], sum = 0;
+        for (int j = 0; j <= cnt; ++j) {
+          double beta = weno_smoothness(o, c, mb, rot[j][k]) + eps;
+          double w = j < cnt ? w0 : w0 * (-cnt) + 1.0;
+          wgt[j] = w / (beta * beta);
+          sum += wgt[j];
+        }
+        for (int j = 0; j <= cnt; ++j) wgt[j] /= sum;
+        for (int i = 0; i < m; ++i) {
+          double v = rot[cnt][k][i] * wgt[cnt];
+          for (int j = 0; j < cnt; ++j) v += rot[j][k][i] * wgt[j];
+          blend[k][i] = v;
+        }
+      }
+      double adj_volume = volume[adj[c * 6 + jf]];
+      for (int k = 0; k < 5; ++k) for (int i = 0; i < m; ++i) {
+        double v = 0;
+        for (int e = 0; e < 5; ++e) v += R[k][e] * blend[e][i];
+        total[k][i] += v * adj_volume;
+      }
+      total_volume += adj_volume;
+    }
+    for (int k = 0; k < 5; ++k) for (int i = 0; i < m; ++i) fresh[(c * 5 + k) * m + i] = total[k][i] / total_volume;
+  }
+  for (int64_t c = 0; c < nc; ++c) {
+    if (!troubled[c]) continue;
+    for (int a = 0; a < n; ++a) {
+      double phi[MAXM];
+      modal_basis_values(o, &basis[c], &o->xyz[(c * n + a) * 3], phi);
+      for (int k = 0; k < 5; ++k) {
+        double v = 0;
+        for (int i = 0; i < m; ++i) v += fresh[(c * 5 + k) * m + i] * phi[i];
+        u[(c * n + a) * 5 + k] = v;
+      }
+    }
+  }
+  free(basis); free(modal); free(fresh); free(volume); free(troubled); free(adj_cnt); free(adj); free(adj_face);
 }
 
 /* one rotated Riemann problem (test hook) */

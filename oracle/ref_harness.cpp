@@ -557,14 +557,17 @@ struct SolverBase {
 };
 
 struct NoLimiter { NoLimiter(double, double) {} };
-template <class Cell, bool kModal> struct LimiterOf { using type = NoLimiter; };
-template <class Cell> struct LimiterOf<Cell, true> { using type = mini::limiter::weno::Lazy<Cell>; };
+template <class Spatial, bool kModal> struct LimiterOf { using type = NoLimiter; };
+// WithLimiter<General, Limiter> keeps a Limiter *limiter_ptr(): recover the type from it
+template <class Spatial> struct LimiterOf<Spatial, true> {
+  using type = std::remove_pointer_t<decltype(std::declval<Spatial &>().limiter_ptr())>;
+};
 
 template <class Spatial>
 struct SolverImpl : SolverBase {
   using Part = typename Spatial::Part;   // OraclePart<Poly>, or OraclePart<Extrapolation<Poly>> under a limiter
   static constexpr bool kLimited = mini::polynomial::Modal<typename Part::Polynomial>;
-  using Limiter = typename LimiterOf<typename Part::Cell, kLimited>::type;
+  using Limiter = typename LimiterOf<Spatial, kLimited>::type;
   GlobalMesh mesh;
   std::unique_ptr<InProcessComm> comm;
   std::vector<std::unique_ptr<Limiter>> limiters;   // one per part: the limiter object is stateful
@@ -586,6 +589,11 @@ struct SolverImpl : SolverBase {
       if constexpr (kLimited) {   // demo/euler/sourceless.cpp:114-120: Spatial(&limiter, &part)
         limiters[r] = std::make_unique<Limiter>(g_weno_w0, g_weno_eps);
         spatials[r] = std::make_unique<Spatial>(limiters[r].get(), parts[r].get());
+        if constexpr (requires(Limiter &l) { l.InstallRiemannSolvers(0); }) {   // weno::Eigen, demo/euler/rotorcraft.cpp:93-96
+          Spatial *sp = spatials[r].get();
+          limiters[r]->InstallRiemannSolvers(
+              [sp](typename Part::Face const &face) -> auto const & { return sp->GetRiemannSolvers(face); });
+        }
       } else if constexpr (std::is_constructible_v<Spatial, Part *, Scalar>) {
         spatials[r] = std::make_unique<Spatial>(parts[r].get(), c_next);   // fr::General(part, c_next)
       } else {
@@ -757,6 +765,12 @@ static SolverBase *Create(int scheme, int riemann, GlobalMesh &&mesh) {
     switch (riemann) {
     case 0: return new SolverImpl<sp::WithLimiter<sp::fr::Lobatto<ModalPart, RExact>, Lazy>>(std::move(mesh));
     case 1: return new SolverImpl<sp::WithLimiter<sp::fr::Lobatto<ModalPart, RHllc>, Lazy>>(std::move(mesh));
+    }
+  } else if (scheme == 5) {   // WithLimiter<fr::Lobatto, weno::Eigen> (demo/euler/rotorcraft.hpp:41 names the limiter so)
+    using Cell = typename ModalPart::Cell;
+    switch (riemann) {
+    case 0: return new SolverImpl<sp::WithLimiter<sp::fr::Lobatto<ModalPart, RExact>, mini::limiter::weno::Eigen<Cell, RExact>>>(std::move(mesh));
+    case 1: return new SolverImpl<sp::WithLimiter<sp::fr::Lobatto<ModalPart, RHllc>, mini::limiter::weno::Eigen<Cell, RHllc>>>(std::move(mesh));
     }
   } else if (scheme == 3) {
     switch (riemann) {

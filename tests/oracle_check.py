@@ -87,9 +87,15 @@ class Oracle:
         lib().oracle_limiter(self.h, C.c_int(kind), _dp(u))
         return u
 
-    def set_limiter(self, w0=0.001, eps=1e-6, on=True):
-        """rk_update then applies weno::Lazy after every stage, like WithLimiter (with_limiter.hpp:57-61)."""
-        lib().oracle_set_limiter(self.h, C.c_int(1 if on else 0), C.c_double(w0), C.c_double(eps))
+    def set_limiter(self, w0=0.001, eps=1e-6, on=True, eigen=False):
+        """rk_update then applies weno::Lazy (or weno::Eigen) after every stage, like WithLimiter
+        (with_limiter.hpp:57-61)."""
+        lib().oracle_set_limiter(self.h, C.c_int((2 if eigen else 1) if on else 0), C.c_double(w0), C.c_double(eps))
+
+    def weno_eigen(self, u, w0=0.001, eps=1e-6):
+        u = np.array(u, dtype=np.float64, copy=True)
+        lib().oracle_weno_eigen(self.h, C.c_double(w0), C.c_double(eps), _dp(u))
+        return u
 
     def weno_lazy(self, u, w0=0.001, eps=1e-6):
         u = np.array(u, dtype=np.float64, copy=True)
