@@ -103,6 +103,12 @@ int mcfd_set_mesh(mcfd_ctx *ctx, int64_t n_nodes, const double *xyz,
                   int64_t n_bfaces, const int64_t *bface_nodes, const int32_t *bface_tags,
                   int64_t n_pairs, const int64_t *periodic_pairs);
 
+/* Optional, before mcfd_set_mesh: the ids of the cells [0, n_local + n_ghost) in the whole (shuffled) mesh, i.e.
+ * Cell::metis_id (part.hpp:190).  The reference makes the cell with the smaller such id the holder of a face between two
+ * local cells (include/mini/mesh/shuffler.hpp:417-420 writes the pairs, part.hpp:932-966 reads them); without the ids the
+ * part-local id decides.  The holder only matters where a face's tangent frame does: mcfd_limiter_weno_eigen. */
+int mcfd_set_cell_global_ids(mcfd_ctx *ctx, int64_t n_cells, const int64_t *ids);
+
 /* Connectivity as the reference numbers it.  kind: 0 local, 1 ghost, 2 boundary faces
  * (part.hpp:115).  Any output pointer may be NULL.  holder/sharer are cell ids (sharer = -1 on
  * boundaries), holder_face/sharer_face local face ids 0..5, orientation the vertex correspondence
@@ -241,6 +247,17 @@ int mcfd_limiter_reconstruct(mcfd_ctx *ctx, int kind);
  * phase 0 = inner cells (they need no ghost data), phase 1 = inter cells (call after mcfd_halo_unpack of the
  * UNLIMITED state, exactly like reconstruct.hpp:46-51; they borrow the already limited inner cells), -1 = both. */
 int mcfd_limiter_weno_lazy(mcfd_ctx *ctx, double w0, double eps, int phase);
+/* The same with limiter = mini::limiter::weno::Eigen<Cell, Riemann>(w0, eps) (include/mini/limiter/weno.hpp:197-349):
+ * only the cells flagged by Eigen::IsNotSmooth (weno.hpp:230-258) are rebuilt, once per adjacent face in the
+ * characteristic variables of that face's frame — the Riemann solver of the face's first quadrature point, as
+ * installed by InstallRiemannSolvers (demo/euler/rotorcraft.cpp:93-96) — with EigenMatrices of the cell mean
+ * (include/mini/riemann/rotated/euler.hpp:330-338, include/mini/riemann/euler/eigen.hpp:27-56), and the per-face
+ * results are averaged with the neighbours' volumes (weno.hpp:331-348). */
+int mcfd_limiter_weno_eigen(mcfd_ctx *ctx, double w0, double eps, int phase);
+/* mini::riemann::euler::EigenMatrices<Gas>(conservative, nu, mu, pi) (include/mini/riemann/euler/eigen.hpp:27-61) for n
+ * states: conservative [n][5], frames [n][9] = (nu, mu, pi); left/right [n][5][5] row-major (L and R).  Test hook. */
+int mcfd_eigen_matrices(mcfd_ctx *ctx, int64_t n, const double *conservative, const double *frames, double *left,
+                        double *right);
 
 int64_t mcfd_launch_count(const mcfd_ctx *ctx);
 /* Duration in ms of the stage kernels launched since the last call with reset != 0, measured with

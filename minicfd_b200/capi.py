@@ -42,6 +42,7 @@ SYMBOLS = {
     "mcfd_set_stream": (C.c_int, [_P, _P]),
     "mcfd_set_mesh": (C.c_int, [_P, C.c_int64, _D, C.c_int64, C.c_int64, _I64, C.c_int64, _I64, _I32,
                                 C.c_int64, _I64]),
+    "mcfd_set_cell_global_ids": (C.c_int, [_P, C.c_int64, _I64]),
     "mcfd_get_faces": (C.c_int64, [_P, C.c_int, _I64, _I64, _I32, _I32, _I32]),
     "mcfd_get_cell_geometry": (C.c_int, [_P, _D, _D]),
     "mcfd_set_halo": (C.c_int, [_P, C.c_int32, _I64, _I64, C.c_int32, _I64, _I64]),
@@ -73,6 +74,8 @@ SYMBOLS = {
     "mcfd_time_step_static": (C.c_int, [C.c_int32, C.c_int32, C.c_int64, _P, _P, C.c_double, C.c_int32, _P, _P]),
     "mcfd_limiter_reconstruct": (C.c_int, [_P, C.c_int]),
     "mcfd_limiter_weno_lazy": (C.c_int, [_P, C.c_double, C.c_double, C.c_int]),
+    "mcfd_limiter_weno_eigen": (C.c_int, [_P, C.c_double, C.c_double, C.c_int]),
+    "mcfd_eigen_matrices": (C.c_int, [_P, C.c_int64, _D, _D, _D, _D]),
     "mcfd_launch_count": (C.c_int64, [_P]),
     "mcfd_enable_kernel_timing": (C.c_int, [_P, C.c_int]),
     "mcfd_kernel_time": (C.c_int, [_P, _D, _I64, C.c_int]),
@@ -137,6 +140,16 @@ class Context:
     def limiter_weno_lazy(self, w0, eps, phase=-1):
         self._check(self.lib.mcfd_limiter_weno_lazy(self.h, w0, eps, phase))
 
+    def limiter_weno_eigen(self, w0, eps, phase=-1):
+        self._check(self.lib.mcfd_limiter_weno_eigen(self.h, w0, eps, phase))
+
+    def eigen_matrices(self, conservative, frames):
+        u = np.ascontiguousarray(conservative, dtype=np.float64).reshape(-1, 5)
+        f = np.ascontiguousarray(frames, dtype=np.float64).reshape(-1, 9)
+        left = np.empty((len(u), 5, 5)); right = np.empty((len(u), 5, 5))
+        self._check(self.lib.mcfd_eigen_matrices(self.h, len(u), _dp(u), _dp(f), _dp(left), _dp(right)))
+        return left, right
+
     def set_diffusion(self, beta_0, beta_1, nu, prandtl):
         self._check(self.lib.mcfd_set_diffusion(self.h, beta_0, beta_1, nu, prandtl))
 
@@ -158,7 +171,10 @@ class Context:
     def set_stream(self, cuda_stream: int):
         self._check(self.lib.mcfd_set_stream(self.h, _P(cuda_stream)))
 
-    def set_mesh(self, nodes, cell_nodes, n_local, n_ghost, bface_nodes, bface_tags, periodic=None):
+    def set_mesh(self, nodes, cell_nodes, n_local, n_ghost, bface_nodes, bface_tags, periodic=None, global_ids=None):
+        if global_ids is not None:
+            ids = np.ascontiguousarray(global_ids, dtype=np.int64)
+            self._check(self.lib.mcfd_set_cell_global_ids(self.h, len(ids), _ip(ids)))
         nodes = np.ascontiguousarray(nodes, dtype=np.float64)
         cell_nodes = np.ascontiguousarray(cell_nodes, dtype=np.int64)
         bface_nodes = np.ascontiguousarray(bface_nodes, dtype=np.int64).reshape(-1, 4)

@@ -976,6 +976,196 @@ MCFD_HD void WenoLazyCell(const WenoArgs &p, int tile, int tl, int comp, const d
   }
 }
 
+// ---- weno::Eigen (limiter/weno.hpp:197-349): the characteristic variant ---------------------------------
+// Same borrowing as weno::Lazy, but only for the cells its jump detector flags, and the blend is done once
+// per adjacent face in the characteristic variables of that face's frame (EigenMatrices of the cell mean),
+// the per-face results averaged with the neighbours' volumes as weights.  The components mix through L and R,
+// so the (cell, component) threads of a tile meet twice per face in scratch memory:
+//   cand  [(slot*5 + comp)*M + k][lane]   slot 0..5 = face, 6 = the cell's own projection
+//   blend [comp*M + k][lane]              the blended characteristic coefficients of the current face
+struct WenoEigenArgs {
+  WenoArgs w;
+  const double *frames;    // [tile][face*9 + i][lane]
+  double *cand, *blend;    // scratch of this CTA
+};
+template <int P>
+struct EigenState {
+  double total[ModalShape<P>::M];
+  double total_volume;
+  int adj_cnt;
+  bool troubled;
+};
+
+// Eigen::IsNotSmooth (weno.hpp:230-258) for my cell; identical in all five component threads.
+template <int Q>
+MCFD_HD bool WenoEigenDetect(const WenoArgs &p, int tile, int tl, const double *quad, int qs, const double *bas, int bs,
+    int *adj_cnt_out) {
+  constexpr int P = Q - 1, N = Q * Q * Q, M = ModalShape<P>::M, kBasRows = ModalShape<P>::kBasRows;
+  const double s00 = bas[(size_t)ModalShape<P>::kSOffset * bs];
+  double volume = 0;
+  for (int n = 0; n < N; ++n) volume += quad[(size_t)(n * 4 + 3) * qs];
+  double mine[2], max_avg[2], sum_diff[2] = {0, 0};
+  for (int t = 0; t < 2; ++t) {
+    const int k = t * 4;
+    const size_t row = ((size_t)tile * 5 * M + k * M) * kTile + tl;
+    mine[t] = p.tay[row];                                   // my polynomial at my centre
+    max_avg[t] = fmax(1e-9, fabs(p.mod[row] * s00));
+  }
+  int adj_cnt = 0;
+  for (int f = 0; f < 6; ++f) {
+    const int nb = p.nbr[((size_t)tile * 6 + f) * kTile + tl];
+    if (nb < 0) continue;
+    ++adj_cnt;
+    const bool holder = (p.code[((size_t)tile * 6 + f) * kTile + tl] & 64) != 0;
+    const double *hv = p.h2s + ((size_t)tile * 18 + f * 3) * kTile + tl;
+    const double sg = holder ? -1.0 : 1.0;                  // my centre seen from the neighbour's
+    const double dn[3] = {sg * hv[0], sg * hv[kTile], sg * hv[2 * kTile]};
+    double tv[M];
+    TaylorValues<P>(dn, tv);
+    const double s00n = p.bas[((size_t)(nb >> 5) * kBasRows + ModalShape<P>::kSOffset) * kTile + (nb & 31)];
+    for (int t = 0; t < 2; ++t) {
+      const int k = t * 4;
+      const size_t row = ((size_t)(nb >> 5) * 5 * M + k * M) * kTile + (nb & 31);
+      double v = 0;
+      for (int i = 0; i < M; ++i) v = fma(p.tay[row + (size_t)i * kTile], tv[i], v);
+      sum_diff[t] += fabs(mine[t] - v);
+      max_avg[t] = fmax(max_avg[t], fabs(p.mod[row] * s00n));
+    }
+  }
+  *adj_cnt_out = adj_cnt;
+  const double divisor = Pow(volume, (P + 1.0) / 2.0 / 3) * adj_cnt;
+  const double reference = P < 3 ? 1.0 : 3.0;
+  return (sum_diff[0] / max_avg[0] / divisor > reference) || (sum_diff[1] / max_avg[1] / divisor > reference);
+}
+
+// Borrow (weno.hpp:269-283): my component of every candidate -> cand scratch
+template <int Q>
+MCFD_HD void WenoEigenBorrow(const WenoEigenArgs &e, int tile, int tl, int comp, const double *quad, int qs,
+    const double *bas, int bs) {
+  constexpr int P = Q - 1, N = Q * Q * Q, M = ModalShape<P>::M;
+  const WenoArgs &p = e.w;
+  const double *S = bas + (size_t)ModalShape<P>::kSOffset * bs;
+  const double s00 = S[0];
+  const double *my_mod = p.mod + ((size_t)tile * 5 * M + comp * M) * kTile + tl;
+  const double my_average = my_mod[0] * s00;
+  for (int f = 0; f < 6; ++f) {
+    const int nb = p.nbr[((size_t)tile * 6 + f) * kTile + tl];
+    if (nb < 0) continue;
+    const bool holder = (p.code[((size_t)tile * 6 + f) * kTile + tl] & 64) != 0;
+    const double *hv = p.h2s + ((size_t)tile * 18 + f * 3) * kTile + tl;
+    const double sg = holder ? 1.0 : -1.0;
+    const double off[3] = {sg * hv[0], sg * hv[kTile], sg * hv[2 * kTile]};
+    const double *nt = p.tay + ((size_t)(nb >> 5) * 5 * M + comp * M) * kTile + (nb & 31);
+    double tb[M], g[M], cand[M];
+    for (int k = 0; k < M; ++k) { tb[k] = nt[(size_t)k * kTile]; g[k] = 0; }
+    for (int n = 0; n < N; ++n) {
+      const double d[3] = {quad[(size_t)(n * 4) * qs], quad[(size_t)(n * 4 + 1) * qs], quad[(size_t)(n * 4 + 2) * qs]};
+      const double dn[3] = {d[0] - off[0], d[1] - off[1], d[2] - off[2]};
+      double tv[M];
+      TaylorValues<P>(dn, tv);
+      double v = 0;
+      for (int k = 0; k < M; ++k) v = fma(tb[k], tv[k], v);
+      v *= quad[(size_t)(n * 4 + 3) * qs];
+      TaylorValues<P>(d, tv);
+      for (int k = 0; k < M; ++k) g[k] = fma(tv[k], v, g[k]);
+    }
+    MomentsToModal<M>(S, bs, g, cand);
+    cand[0] += (my_average - cand[0] * s00) / s00;
+    double *dst = e.cand + ((size_t)(f * 5 + comp) * M) * kTile + tl;
+    for (int k = 0; k < M; ++k) dst[(size_t)k * kTile] = cand[k];
+  }
+  double *dst = e.cand + ((size_t)(6 * 5 + comp) * M) * kTile + tl;
+  for (int k = 0; k < M; ++k) dst[(size_t)k * kTile] = my_mod[(size_t)k * kTile];
+}
+
+// ReconstructOnFace, first half (weno.hpp:290-330): characteristic component `comp` of every candidate, its
+// smoothness, the weights, the blend -> blend scratch
+template <int Q>
+MCFD_HD void WenoEigenFaceBlend(const WenoEigenArgs &e, int tile, int tl, int comp, int face, int adj_cnt,
+    const double *quad, int qs, const double *bas, int bs) {
+  constexpr int P = Q - 1, M = ModalShape<P>::M;
+  const WenoArgs &p = e.w;
+  const double s00 = bas[(size_t)ModalShape<P>::kSOffset * bs];
+  double big_u[5], frame[9], row[5];
+  for (int c = 0; c < 5; ++c) big_u[c] = p.mod[((size_t)tile * 5 * M + c * M) * kTile + tl] * s00;
+  for (int i = 0; i < 9; ++i) frame[i] = e.frames[((size_t)tile * 54 + face * 9 + i) * kTile + tl];
+  const EigenCommon ec = EigenPrepare(big_u, frame);
+  EigenRowL(ec, frame, comp, row);
+  double blend[M], sum_w = 0;
+  for (int k = 0; k < M; ++k) blend[k] = 0;
+  for (int slot = 0; slot < 7; ++slot) {
+    if (slot < 6 && p.nbr[((size_t)tile * 6 + slot) * kTile + tl] < 0) continue;
+    double rot[M];
+    for (int k = 0; k < M; ++k) {
+      double v = 0;
+      for (int c = 0; c < 5; ++c) v = fma(row[c], e.cand[((size_t)(slot * 5 + c) * M + k) * kTile + tl], v);
+      rot[k] = v;
+    }
+    const double beta = WenoSmoothness<Q>(rot, quad, qs, bas, bs) + p.eps;
+    const double w = (slot < 6 ? p.w0 : p.w0 * (-adj_cnt) + 1.0) / (beta * beta);
+    sum_w += w;
+    for (int k = 0; k < M; ++k) blend[k] = fma(w, rot[k], blend[k]);
+  }
+  const double inv = 1.0 / sum_w;
+  double *dst = e.blend + ((size_t)comp * M) * kTile + tl;
+  for (int k = 0; k < M; ++k) dst[(size_t)k * kTile] = blend[k] * inv;
+}
+
+// ReconstructOnFace, second half (weno.hpp:331-337): back to conservative variables, weighted by the
+// neighbour's volume
+template <int Q>
+MCFD_HD void WenoEigenFaceAccumulate(const WenoEigenArgs &e, int tile, int tl, int comp, int face, const double *bas,
+    int bs, EigenState<Q - 1> *st) {
+  constexpr int P = Q - 1, M = ModalShape<P>::M, kBasRows = ModalShape<P>::kBasRows;
+  const WenoArgs &p = e.w;
+  const double s00 = bas[(size_t)ModalShape<P>::kSOffset * bs];
+  double big_u[5], frame[9], row[5];
+  for (int c = 0; c < 5; ++c) big_u[c] = p.mod[((size_t)tile * 5 * M + c * M) * kTile + tl] * s00;
+  for (int i = 0; i < 9; ++i) frame[i] = e.frames[((size_t)tile * 54 + face * 9 + i) * kTile + tl];
+  const EigenCommon ec = EigenPrepare(big_u, frame);
+  EigenRowR(ec, frame, comp, row);
+  const int nb = p.nbr[((size_t)tile * 6 + face) * kTile + tl];
+  const double s00n = p.bas[((size_t)(nb >> 5) * kBasRows + ModalShape<P>::kSOffset) * kTile + (nb & 31)];
+  const double adj_volume = 1.0 / (s00n * s00n);
+  for (int k = 0; k < M; ++k) {
+    double v = 0;
+    for (int c = 0; c < 5; ++c) v = fma(row[c], e.blend[((size_t)c * M + k) * kTile + tl], v);
+    st->total[k] = fma(v, adj_volume, st->total[k]);
+  }
+  st->total_volume += adj_volume;
+}
+
+// weno.hpp:342-348 + Extrapolation::SetCoeff: normalise, publish the new coefficients, resample the nodes;
+// cells the detector left alone only pass their coefficients on
+template <int Q>
+MCFD_HD void WenoEigenFinish(const WenoEigenArgs &e, int tile, int tl, int comp, const double *quad, int qs,
+    const double *bas, int bs, const EigenState<Q - 1> &st) {
+  constexpr int P = Q - 1, N = Q * Q * Q, F = 5 * N, M = ModalShape<P>::M;
+  const WenoArgs &p = e.w;
+  const size_t row = ((size_t)tile * 5 * M + comp * M) * kTile + tl;
+  if (!st.troubled) {
+    for (int k = 0; k < M; ++k) {
+      p.mod_new[row + (size_t)k * kTile] = p.mod[row + (size_t)k * kTile];
+      p.tay_new[row + (size_t)k * kTile] = p.tay[row + (size_t)k * kTile];
+    }
+    return;
+  }
+  double fresh[M], t[M];
+  const double inv = 1.0 / st.total_volume;
+  for (int k = 0; k < M; ++k) fresh[k] = st.total[k] * inv;
+  ModalToTaylor<M>(bas + (size_t)ModalShape<P>::kSOffset * bs, bs, fresh, t);
+  for (int k = 0; k < M; ++k) { p.mod_new[row + (size_t)k * kTile] = fresh[k]; p.tay_new[row + (size_t)k * kTile] = t[k]; }
+  double *dst = p.u + (size_t)tile * F * kTile + tl;
+  for (int n = 0; n < N; ++n) {
+    const double d[3] = {quad[(size_t)(n * 4) * qs], quad[(size_t)(n * 4 + 1) * qs], quad[(size_t)(n * 4 + 2) * qs]};
+    double tv[M];
+    TaylorValues<P>(d, tv);
+    double v = 0;
+    for (int k = 0; k < M; ++k) v = fma(t[k], tv[k], v);
+    dst[(size_t)(n * 5 + comp) * kTile] = v;
+  }
+}
+
 #ifdef __CUDACC__
 // One CTA per tile, five warps: warp = component, lanes = cells.  Quadrature offsets/weights and the
 // cell's basis are staged in shared memory by all warps first.
@@ -1020,6 +1210,51 @@ __global__ void __launch_bounds__(160) WenoLazyKernel(WenoArgs p, int tile_begin
   const int cell = tile * kTile + lane;
   if (cell < p.cell_begin || cell >= p.cell_end) return;
   WenoLazyCell<Q>(p, tile, lane, comp, sQuad + lane, kTile, sBas + lane, kTile);
+}
+// weno::Eigen: persistent CTAs (each owns one scratch slot) walking over the tiles of the batch
+template <int Q>
+struct WenoEigenShape {
+  static constexpr int M = ModalShape<Q - 1>::M;
+  static constexpr size_t kScratchDoubles = (size_t)(7 * 5 * M + 5 * M) * kTile;   // per CTA
+};
+template <int Q>
+__global__ void __launch_bounds__(160) WenoEigenKernel(WenoEigenArgs e, double *scratch, int tile_begin, int tile_end) {
+  constexpr int P = Q - 1, N = Q * Q * Q, M = ModalShape<P>::M;
+  extern __shared__ double smem[];
+  double *sQuad = smem, *sBas = smem + N * 4 * kTile;
+  const int lane = threadIdx.x & 31, comp = threadIdx.x >> 5;
+  e.cand = scratch + (size_t)blockIdx.x * WenoEigenShape<Q>::kScratchDoubles;
+  e.blend = e.cand + (size_t)7 * 5 * M * kTile;
+  for (int tile = tile_begin + blockIdx.x; tile < tile_end; tile += gridDim.x) {
+    __syncthreads();                       // the previous tile's shared tables are no longer read
+    WenoStage<Q>(e.w.geom, e.w.bas, tile, sQuad, sBas);
+    const int cell = tile * kTile + lane;
+    const bool active = cell >= e.w.cell_begin && cell < e.w.cell_end;
+    EigenState<P> st;
+    st.total_volume = 0; st.adj_cnt = 0; st.troubled = false;
+    for (int k = 0; k < M; ++k) st.total[k] = 0;
+    if (active) st.troubled = WenoEigenDetect<Q>(e.w, tile, lane, sQuad + lane, kTile, sBas + lane, kTile, &st.adj_cnt);
+    if (active && st.troubled) WenoEigenBorrow<Q>(e, tile, lane, comp, sQuad + lane, kTile, sBas + lane, kTile);
+    __syncthreads();
+    for (int f = 0; f < 6; ++f) {
+      const bool work = active && st.troubled && e.w.nbr[((size_t)tile * 6 + f) * kTile + lane] >= 0;
+      if (work) WenoEigenFaceBlend<Q>(e, tile, lane, comp, f, st.adj_cnt, sQuad + lane, kTile, sBas + lane, kTile);
+      __syncthreads();
+      if (work) WenoEigenFaceAccumulate<Q>(e, tile, lane, comp, f, sBas + lane, kTile, &st);
+      __syncthreads();
+    }
+    if (active) WenoEigenFinish<Q>(e, tile, lane, comp, sQuad + lane, kTile, sBas + lane, kTile, st);
+  }
+}
+// EigenMatrices of n states (test hook for SURVEY row a28): L and R row-major [n][5][5]
+__global__ void EigenMatricesKernel(int n, const double *cons, const double *frames, double *L, double *R) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const EigenCommon ec = EigenPrepare(cons + i * 5, frames + i * 9);
+  for (int k = 0; k < 5; ++k) {
+    EigenRowL(ec, frames + i * 9, k, L + (size_t)i * 25 + k * 5);
+    EigenRowR(ec, frames + i * 9, k, R + (size_t)i * 25 + k * 5);
+  }
 }
 // new coefficients of the cells of a finished batch -> the tables the next batch borrows from
 __global__ void CopyCellRowsKernel(const double *src, double *dst, int rows, int cell_begin, int cell_end) {

@@ -1,4 +1,5 @@
 // libmcfd.cu — the C ABI of include/minicfd_b200.h on top of kernels.cuh.
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include <memory>
@@ -53,6 +54,8 @@ struct mcfd_ctx {
   DevBuf<double> u[3], res, geom, bvals, length, column;
   DevBuf<double> grad, hn, h2s;                 // viscous traces (TraceKernel) and HolderToSharer vectors
   DevBuf<double> bas, mod, tay, mod_new, tay_new;   // WENO limiter: per-cell bases and modal coefficients
+  DevBuf<double> frames, weno_scratch;          // weno::Eigen: face frames, per-CTA candidate scratch
+  std::vector<int64_t> global_ids;              // optional, for the next mcfd_set_mesh
   int64_t first_inter = 0;                      // local cells [first_inter, n_local) have a ghost neighbour
   Viscosity vis{2.0, 1.0 / 12, 0.0, 0.0};       // Direct::SetBetaValues / NavierStokes::SetProperty
   double prandtl = 0.708;
@@ -82,6 +85,27 @@ int Fail(mcfd_ctx *ctx, int status, std::string msg) {
   if (ctx) ctx->error = std::move(msg);
   else g_create_error = std::move(msg);
   return status;
+}
+
+// The per-degree tables live in ONE __constant__ symbol per device while every context owns its own copy
+// (degree, scheme, launch shape and Vincent parameter differ between contexts).  Before a context launches a
+// kernel that reads them, the symbol is brought in line with that context, stream-ordered on the context's
+// stream.  Contexts with different tables must therefore not run kernels concurrently on different streams.
+Tables g_device_tables[64];
+bool g_device_tables_valid[64] = {false};
+
+cudaError_t EnsureTables(mcfd_ctx *ctx) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+  if (g_device_tables_valid[dev] && std::memcmp(&g_device_tables[dev], &ctx->tables, sizeof(Tables)) == 0)
+    return cudaSuccess;
+  e = cudaMemcpyToSymbolAsync(c_tab, &ctx->tables, sizeof(Tables), 0, cudaMemcpyHostToDevice, ctx->stream);
+  if (e != cudaSuccess) return e;
+  g_device_tables[dev] = ctx->tables;
+  g_device_tables_valid[dev] = true;
+  return cudaSuccess;
 }
 
 #define MCFD_CUDA(ctx, call)                                                          \
@@ -135,7 +159,8 @@ cudaError_t LaunchStageViscous(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) 
 int LaunchTrace(mcfd_ctx *ctx, const double *u, int64_t cell_begin, int64_t cell_end) {
   if (cell_end <= cell_begin) return MCFD_OK;
   const int tile_begin = (int)(cell_begin / kTile), tile_end = (int)((cell_end + kTile - 1) / kTile);
-  cudaError_t e;
+  cudaError_t e = EnsureTables(ctx);
+  if (e != cudaSuccess) return Fail(ctx, MCFD_ERR_CUDA, cudaGetErrorString(e));
   if (ctx->q == 3) {
     TraceKernel<3><<<tile_end - tile_begin, TraceShape<3>::NW * 32, TraceShape<3>::kSharedBytes, ctx->stream>>>(u, ctx->geom.p,
         ctx->grad.p, ctx->hn.p, tile_begin, (int)cell_begin, (int)cell_end);
@@ -170,6 +195,7 @@ int LaunchStage(mcfd_ctx *ctx, const double *u_in, const double *u0, double *u_o
   a.mode = mode; a.dt = dt; a.dt_dev = ctx->rk_order ? ctx->rk_dt_dev : nullptr;
   a.grad = ctx->grad.p; a.hn = ctx->hn.p; a.h2s = ctx->h2s.p; a.vis = ctx->vis;
   int n_blocks = (int)(block_end - block_begin);
+  MCFD_CUDA(ctx, EnsureTables(ctx));
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (ctx->timing) {
     if (ctx->events_used == ctx->events.size()) {
@@ -295,8 +321,6 @@ int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
   ctx->cpb = (ctx->q == 3) ? kP2Cells : kP3Cells;
   ctx->n_warps = (ctx->q == 3) ? (config->diffusion != MCFD_INVISCID ? kP2ViscousWarps : kP2Warps) : kP3Warps;
   ctx->tables = BuildTables(config->degree, config->scheme, ctx->n_warps, kTile / ctx->cpb, config->fr_c_next);
-  e = cudaMemcpyToSymbol(c_tab, &ctx->tables, sizeof(Tables));
-  if (e != cudaSuccess) return Fail(nullptr, MCFD_ERR_CUDA, cudaGetErrorString(e));
   e = ctx->dt_bits.Alloc(1);
   if (e != cudaSuccess) return Fail(nullptr, MCFD_ERR_CUDA, cudaGetErrorString(e));
   *ctx_out = ctx.release();
@@ -326,9 +350,12 @@ int mcfd_set_mesh(mcfd_ctx *ctx, int64_t n_nodes, const double *xyz, int64_t n_l
   if (!ctx || !xyz || !cell_nodes || n_local <= 0 || n_ghost < 0)
     return Fail(ctx, MCFD_ERR_ARG, "bad mesh arguments");
   if (n_local + n_ghost > (int64_t)1 << 30) return Fail(ctx, MCFD_ERR_ARG, "too many cells for int32 ids");
-  // the tables are per context but live in one __constant__ symbol: refresh
-  MCFD_CUDA(ctx, cudaMemcpyToSymbol(c_tab, &ctx->tables, sizeof(Tables)));
   ctx->mesh = HostMesh();
+  if (!ctx->global_ids.empty()) {
+    if ((int64_t)ctx->global_ids.size() != n_local + n_ghost)
+      return Fail(ctx, MCFD_ERR_ARG, "mcfd_set_cell_global_ids was given a different number of cells");
+    ctx->mesh.global_ids = ctx->global_ids;
+  }
   if (!ctx->mesh.Build(ctx->cfg.degree, n_nodes, xyz, n_local, n_ghost, cell_nodes, n_bfaces,
           bface_nodes, bface_tags, n_pairs, periodic_pairs))
     return Fail(ctx, MCFD_ERR_MESH, ctx->mesh.error);
@@ -356,7 +383,7 @@ int mcfd_set_mesh(mcfd_ctx *ctx, int64_t n_nodes, const double *xyz, int64_t n_l
     MCFD_CUDA(ctx, ctx->h2s.Alloc(h2s.size()));
     MCFD_CUDA(ctx, cudaMemcpy(ctx->h2s.p, h2s.data(), h2s.size() * sizeof(double), cudaMemcpyHostToDevice));
   }
-  ctx->bas.Free();
+  ctx->bas.Free(); ctx->frames.Free(); ctx->weno_scratch.Free();
   if (ctx->cfg.diffusion != MCFD_INVISCID) {
     MCFD_CUDA(ctx, ctx->grad.Alloc((size_t)ctx->n_tiles * ctx->n_nodes * 15 * kTile));
     MCFD_CUDA(ctx, ctx->hn.Alloc((size_t)ctx->n_tiles * 6 * ctx->q * ctx->q * 15 * kTile));
@@ -388,6 +415,12 @@ int mcfd_set_mesh(mcfd_ctx *ctx, int64_t n_nodes, const double *xyz, int64_t n_l
   ctx->send_cells.Free(); ctx->recv_cells.Free(); ctx->send_buf.Free(); ctx->recv_buf.Free();
   ctx->cur = 0;
   ctx->has_mesh = true;
+  return MCFD_OK;
+}
+
+int mcfd_set_cell_global_ids(mcfd_ctx *ctx, int64_t n_cells, const int64_t *ids) {
+  if (!ctx || n_cells < 0 || (n_cells > 0 && !ids)) return Fail(ctx, MCFD_ERR_ARG, "bad arguments");
+  ctx->global_ids.assign(ids, ids + n_cells);
   return MCFD_OK;
 }
 
@@ -710,6 +743,7 @@ int mcfd_limiter_reconstruct(mcfd_ctx *ctx, int kind) {
   if (kind != 0 && kind != 1) return Fail(ctx, MCFD_ERR_ARG, "limiter kind must be 0 (average) or 1 (majority)");
   if (ctx->rk_order) return Fail(ctx, MCFD_ERR_STATE, "an RK step is open");
   int n = (int)ctx->mesh.n_local, threads = 128, blocks = (n + threads - 1) / threads;
+  MCFD_CUDA(ctx, EnsureTables(ctx));
   if (ctx->q == 3) CellConstantKernel<3><<<blocks, threads, 0, ctx->stream>>>(ctx->u[ctx->cur].p, ctx->geom.p, n, kind);
   else CellConstantKernel<4><<<blocks, threads, 0, ctx->stream>>>(ctx->u[ctx->cur].p, ctx->geom.p, n, kind);
   MCFD_CUDA(ctx, cudaGetLastError());
@@ -721,17 +755,21 @@ int mcfd_limiter_reconstruct(mcfd_ctx *ctx, int kind) {
 
 namespace {
 
+constexpr int kWenoEigenCtas = 296;   // persistent CTAs of the weno::Eigen kernel, one scratch slot each
+
 template <int Q>
 int WenoLazyBatch(mcfd_ctx *ctx, double *u, double w0, double eps, int64_t modal_begin, int64_t modal_end,
-    int64_t cell_begin, int64_t cell_end, bool publish) {
+    int64_t cell_begin, int64_t cell_end, bool publish, bool eigen) {
   constexpr int M = ModalShape<Q - 1>::M;
   const size_t smem = WenoShape<Q>::kSharedBytes;
   static bool configured = false;
   if (!configured) {
     MCFD_CUDA(ctx, cudaFuncSetAttribute(ModalKernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     MCFD_CUDA(ctx, cudaFuncSetAttribute(WenoLazyKernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    MCFD_CUDA(ctx, cudaFuncSetAttribute(WenoEigenKernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = true;
   }
+  MCFD_CUDA(ctx, EnsureTables(ctx));
   if (modal_end > modal_begin) {   // Extrapolation::UpdateModalCoeff of the cells whose nodal values are new
     const int t0 = (int)(modal_begin / kTile), t1 = (int)((modal_end + kTile - 1) / kTile);
     ModalKernel<Q><<<t1 - t0, 160, smem, ctx->stream>>>(u, ctx->geom.p, ctx->bas.p, ctx->mod.p, ctx->tay.p, t0,
@@ -744,7 +782,14 @@ int WenoLazyBatch(mcfd_ctx *ctx, double *u, double w0, double eps, int64_t modal
     a.mod = ctx->mod.p; a.tay = ctx->tay.p; a.mod_new = ctx->mod_new.p; a.tay_new = ctx->tay_new.p;
     a.cell_begin = (int)cell_begin; a.cell_end = (int)cell_end; a.w0 = w0; a.eps = eps;
     const int t0 = (int)(cell_begin / kTile), t1 = (int)((cell_end + kTile - 1) / kTile);
-    WenoLazyKernel<Q><<<t1 - t0, 160, smem, ctx->stream>>>(a, t0);
+    if (eigen) {
+      WenoEigenArgs e;
+      e.w = a; e.frames = ctx->frames.p; e.cand = nullptr; e.blend = nullptr;
+      const int grid = std::min(t1 - t0, kWenoEigenCtas);
+      WenoEigenKernel<Q><<<grid, 160, smem, ctx->stream>>>(e, ctx->weno_scratch.p, t0, t1);
+    } else {
+      WenoLazyKernel<Q><<<t1 - t0, 160, smem, ctx->stream>>>(a, t0);
+    }
     ctx->launches++;
     if (publish) {   // the next batch borrows the limited polynomials of this one (limiter/reconstruct.hpp:41-51)
       const int n = (int)(cell_end - cell_begin), threads = 128, blocks = (n + threads - 1) / threads;
@@ -761,7 +806,36 @@ int WenoLazyBatch(mcfd_ctx *ctx, double *u, double w0, double eps, int64_t modal
 
 extern "C" {
 
+static int LimiterWeno(mcfd_ctx *ctx, double w0, double eps, int phase, bool eigen);
+
 int mcfd_limiter_weno_lazy(mcfd_ctx *ctx, double w0, double eps, int phase) {
+  return LimiterWeno(ctx, w0, eps, phase, false);
+}
+
+int mcfd_limiter_weno_eigen(mcfd_ctx *ctx, double w0, double eps, int phase) {
+  return LimiterWeno(ctx, w0, eps, phase, true);
+}
+
+int mcfd_eigen_matrices(mcfd_ctx *ctx, int64_t n, const double *conservative, const double *frames, double *left,
+    double *right) {
+  if (!ctx || n <= 0 || !conservative || !frames || !left || !right) return MCFD_ERR_ARG;
+  DevBuf<double> du, df, dl, dr;
+  MCFD_CUDA(ctx, du.Alloc(5 * n));
+  MCFD_CUDA(ctx, df.Alloc(9 * n));
+  MCFD_CUDA(ctx, dl.Alloc(25 * n));
+  MCFD_CUDA(ctx, dr.Alloc(25 * n));
+  MCFD_CUDA(ctx, cudaMemcpy(du.p, conservative, 5 * n * sizeof(double), cudaMemcpyHostToDevice));
+  MCFD_CUDA(ctx, cudaMemcpy(df.p, frames, 9 * n * sizeof(double), cudaMemcpyHostToDevice));
+  EigenMatricesKernel<<<(int)((n + 127) / 128), 128, 0, ctx->stream>>>((int)n, du.p, df.p, dl.p, dr.p);
+  MCFD_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  MCFD_CUDA(ctx, cudaMemcpy(left, dl.p, 25 * n * sizeof(double), cudaMemcpyDeviceToHost));
+  MCFD_CUDA(ctx, cudaMemcpy(right, dr.p, 25 * n * sizeof(double), cudaMemcpyDeviceToHost));
+  return MCFD_OK;
+}
+
+static int LimiterWeno(mcfd_ctx *ctx, double w0, double eps, int phase, bool eigen) {
   if (int s = RequireMesh(ctx)) return s;
   if (phase < -1 || phase > 1) return Fail(ctx, MCFD_ERR_ARG, "phase must be -1 (both), 0 (inner cells) or 1 (inter cells)");
   const int m = ctx->q == 3 ? 10 : 20, rows = ctx->q == 3 ? ModalShape<2>::kBasRows : ModalShape<3>::kBasRows;
@@ -775,11 +849,18 @@ int mcfd_limiter_weno_lazy(mcfd_ctx *ctx, double w0, double eps, int phase) {
       MCFD_CUDA(ctx, cudaMemset(b->p, 0, n * sizeof(double)));
     }
   }
+  if (eigen && !ctx->frames.p) {
+    auto frames = ToTiles(ctx->mesh.frames, 54, ctx->n_cells, ctx->n_tiles);
+    MCFD_CUDA(ctx, ctx->frames.Alloc(frames.size()));
+    MCFD_CUDA(ctx, cudaMemcpy(ctx->frames.p, frames.data(), frames.size() * sizeof(double), cudaMemcpyHostToDevice));
+    const size_t per_cta = ctx->q == 3 ? WenoEigenShape<3>::kScratchDoubles : WenoEigenShape<4>::kScratchDoubles;
+    MCFD_CUDA(ctx, ctx->weno_scratch.Alloc(per_cta * kWenoEigenCtas));
+  }
   double *u = HaloState(ctx);
   const int64_t nl = ctx->mesh.n_local, nc = ctx->n_cells, fi = ctx->mesh.n_ghost ? ctx->first_inter : nl;
   auto batch = [&](int64_t mb, int64_t me, int64_t cb, int64_t ce, bool publish) {
-    return ctx->q == 3 ? WenoLazyBatch<3>(ctx, u, w0, eps, mb, me, cb, ce, publish)
-                       : WenoLazyBatch<4>(ctx, u, w0, eps, mb, me, cb, ce, publish);
+    return ctx->q == 3 ? WenoLazyBatch<3>(ctx, u, w0, eps, mb, me, cb, ce, publish, eigen)
+                       : WenoLazyBatch<4>(ctx, u, w0, eps, mb, me, cb, ce, publish, eigen);
   };
   if (phase != 1) {   // act(inner cells): needs no ghost cell (limiter/reconstruct.hpp:46-48)
     if (int s = batch(0, nl, 0, fi, fi < nl)) return s;

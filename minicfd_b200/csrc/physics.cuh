@@ -564,5 +564,57 @@ MCFD_HD void NsMinusFluxNoSlip(const Viscosity &vis, const double *wall, const d
   NsMinusFluxCore(vis, u[0], gv, nx, ny, nz, wall[1], wall[2], wall[3], wall[4], flux);
 }
 
+// ---- EigenMatrices (riemann/euler/eigen.hpp:27-56) -----------------------------------------------
+// Left / right eigenvector matrices of the Euler flux Jacobian of the conservative state `u` along the
+// frame (nu, mu, pi) = f[0..2], f[3..5], f[6..8].  Row k of L and row c of R are all a thread of the
+// characteristic limiter needs.
+struct EigenCommon {
+  double ux, uy, uz, u_nu, u_mu, u_pi, a, ek, h0, b1, b2;
+};
+MCFD_HD EigenCommon EigenPrepare(const double *u, const double *f) {
+  const Prim q = ConsToPrim(u[0], u[1], u[2], u[3], u[4]);
+  EigenCommon e;
+  e.ux = q.u; e.uy = q.v; e.uz = q.w;
+  e.u_nu = q.u * f[0] + q.v * f[1] + q.w * f[2];
+  e.u_mu = q.u * f[3] + q.v * f[4] + q.w * f[5];
+  e.u_pi = q.u * f[6] + q.v * f[7] + q.w * f[8];
+  e.a = SoundSpeed(q.rho, q.p);
+  e.ek = (q.u * q.u + q.v * q.v + q.w * q.w) / 2;
+  const double e0 = e.a * e.a * kOneOverGm1;
+  e.h0 = e0 + e.ek;
+  e.b1 = 1 / e0;
+  e.b2 = e.b1 * e.ek;
+  return e;
+}
+MCFD_HD void EigenRowL(const EigenCommon &e, const double *f, int k, double *row) {
+  const double vel[3] = {e.ux, e.uy, e.uz};
+  if (k == 0 || k == 4) {
+    const double s = k == 0 ? 1.0 : -1.0;
+    row[0] = (e.b2 + s * e.u_nu / e.a) / 2;
+    for (int x = 0; x < 3; ++x) row[1 + x] = -(e.b1 * vel[x] + s * f[x] / e.a) / 2;
+    row[4] = e.b1 / 2;
+  } else if (k == 1) {
+    row[0] = 1 - e.b2;
+    for (int x = 0; x < 3; ++x) row[1 + x] = e.b1 * vel[x];
+    row[4] = -e.b1;
+  } else {
+    const double *t = f + (k == 2 ? 3 : 6);
+    row[0] = k == 2 ? -e.u_mu : -e.u_pi;
+    for (int x = 0; x < 3; ++x) row[1 + x] = t[x];
+    row[4] = 0;
+  }
+}
+MCFD_HD void EigenRowR(const EigenCommon &e, const double *f, int c, double *row) {
+  if (c == 0) {
+    row[0] = 1; row[1] = 1; row[2] = 0; row[3] = 0; row[4] = 1;
+  } else if (c == 4) {
+    row[0] = e.h0 - e.a * e.u_nu; row[1] = e.ek; row[2] = e.u_mu; row[3] = e.u_pi; row[4] = e.h0 + e.a * e.u_nu;
+  } else {
+    const int x = c - 1;
+    const double v = x == 0 ? e.ux : (x == 1 ? e.uy : e.uz);
+    row[0] = v - e.a * f[x]; row[1] = v; row[2] = f[3 + x]; row[3] = f[6 + x]; row[4] = v + e.a * f[x];
+  }
+}
+
 }  // namespace mcfd
 #endif  // MINICFD_B200_PHYSICS_CUH_

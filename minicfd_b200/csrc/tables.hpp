@@ -233,7 +233,12 @@ struct HostMesh {
   std::vector<double> coef;          // [cell][21]
   std::vector<double> c0;            // [cell][3] constant term of the map = x(0,0,0)
   std::vector<double> h2s;           // [cell][6][3] Face::HolderToSharer of the face behind local face f
+  std::vector<double> frames;        // [cell][6][9] normal frame (normal, tangent, bitangent) of that face at its
+                                     // quadrature point 0, as rotated::Euler::Rotate receives it (fem.hpp:103-106)
   std::vector<double> length, volume;  // local cells
+  // optional: the cells' ids in the whole mesh.  The reference decides holder / sharer of a face between two
+  // local cells by those (holder = smaller id, mesh/shuffler.hpp:417-420), not by the part-local numbering.
+  std::vector<int64_t> global_ids;
   std::string error;
 
   using Key = std::array<int64_t, 4>;
@@ -372,7 +377,8 @@ struct HostMesh {
     for (auto &[key, list] : sides) {
       if (list.size() == 2) {
         Side h = list[0], s = list[1];
-        if (s.cell < h.cell) std::swap(h, s);
+        const bool both_local = h.cell < nl && s.cell < nl && (int64_t)global_ids.size() == nc;
+        if (both_local ? global_ids[s.cell] < global_ids[h.cell] : s.cell < h.cell) std::swap(h, s);
         if (h.cell >= nl) continue;  // ghost-ghost
         int pi[4];
         for (int m = 0; m < 4; ++m) {
@@ -389,7 +395,14 @@ struct HostMesh {
         return false;
       }
     }
-    std::sort(all.begin(), all.end(), [](FaceRec const &a, FaceRec const &b) {
+    const bool have_ids = (int64_t)global_ids.size() == nc;
+    std::sort(all.begin(), all.end(), [&](FaceRec const &a, FaceRec const &b) {
+      const bool ga = a.sharer >= nl, gb = b.sharer >= nl;   // ghost faces keep the part-local order
+      if (ga != gb) return gb;
+      if (have_ids && !ga) {
+        const int64_t ah = global_ids[a.holder], bh = global_ids[b.holder];
+        return ah != bh ? ah < bh : global_ids[a.sharer] < global_ids[b.sharer];
+      }
       return a.holder != b.holder ? a.holder < b.holder : a.sharer < b.sharer;
     });
     for (auto &fr : all) {
@@ -502,6 +515,37 @@ struct HostMesh {
       }
     };
     set_faces(local_faces); set_faces(ghost_faces); set_faces(bound_faces);
+    // Face frames at face point 0 = the holder's first face corner (Lobatto points include the ends):
+    // tangent along corner 0 -> 1, normal = d/da x d/db (coordinate/face.hpp:54-62, quadrangle.hpp:77-105)
+    frames.assign(nc * 54, 0.0);
+    auto set_frames = [&](std::vector<FaceRec> const &faces) {
+      for (auto const &fr : faces) {
+        const double *P[4];
+        for (int m = 0; m < 4; ++m) P[m] = &xyz[cn[fr.holder * 8 + kFaceNodes[fr.holder_face][m]] * 3];
+        const double a = x[0], b = x[0];
+        double ja[3] = {0, 0, 0}, jb[3] = {0, 0, 0};
+        for (int m = 0; m < 4; ++m) {
+          const double fa = 1 + kCorner[m][0] * a, fb = 1 + kCorner[m][1] * b;
+          for (int k = 0; k < 3; ++k) {
+            ja[k] += kCorner[m][0] * (fb / 4) * P[m][k];
+            jb[k] += kCorner[m][1] * (fa / 4) * P[m][k];
+          }
+        }
+        double f9[9];
+        double nn[3] = {ja[1] * jb[2] - ja[2] * jb[1], ja[2] * jb[0] - ja[0] * jb[2], ja[0] * jb[1] - ja[1] * jb[0]};
+        const double ln = std::sqrt(nn[0] * nn[0] + nn[1] * nn[1] + nn[2] * nn[2]);
+        const double la = std::sqrt(ja[0] * ja[0] + ja[1] * ja[1] + ja[2] * ja[2]);
+        for (int k = 0; k < 3; ++k) { f9[k] = nn[k] / ln; f9[3 + k] = ja[k] / la; }
+        f9[6] = f9[1] * f9[5] - f9[2] * f9[4];
+        f9[7] = f9[2] * f9[3] - f9[0] * f9[5];
+        f9[8] = f9[0] * f9[4] - f9[1] * f9[3];
+        for (int k = 0; k < 9; ++k) {
+          frames[(fr.holder * 6 + fr.holder_face) * 9 + k] = f9[k];
+          if (fr.sharer >= 0) frames[(fr.sharer * 6 + fr.sharer_face) * 9 + k] = f9[k];
+        }
+      }
+    };
+    set_frames(local_faces); set_frames(ghost_faces); set_frames(bound_faces);
     return true;
   }
 };

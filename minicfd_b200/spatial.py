@@ -22,7 +22,7 @@ class Spatial:
         self.kfields = self.ctx.kfields
         m = part.mesh
         self.ctx.set_mesh(m.nodes, part.cell_nodes, part.n_local, part.n_ghost, part.bfaces, part.btags,
-                          m.periodic)
+                          m.periodic, global_ids=part.global_ids)
         if part.n_ghost:
             self.ctx.set_halo([len(c) for c in part.send_cells],
                               np.concatenate(part.send_cells) if part.send_cells else [],
@@ -74,11 +74,13 @@ class Spatial:
         demo/laminar/cavity.cpp:30-38; ignored by inviscid systems (fr/general.hpp:455-459)."""
         self._set_bc(tag, capi.BC_NO_SLIP_WALL, func, time_dependent)
 
-    def SetLimiter(self, w0=0.001, eps=1e-6):
+    def SetLimiter(self, w0=0.001, eps=1e-6, eigen=False):
         """Makes this object behave like `WithLimiter<General, limiter::weno::Lazy<Cell>>(&limiter, &part)` with
         `limiter(w0, eps)` (spatial/with_limiter.hpp:21-68, demo/euler/sourceless.cpp:114-120): the limiter runs
-        after every SetSolutionColumn / Approximate and after every Runge-Kutta stage.  None switches it off."""
+        after every SetSolutionColumn / Approximate and after every Runge-Kutta stage.  None switches it off;
+        eigen=True selects `weno::Eigen<Cell, Riemann>` (the characteristic variant with its jump detector)."""
         self._limiter = None if w0 is None else (float(w0), float(eps))
+        self._limit_call = self.ctx.limiter_weno_eigen if eigen else self.ctx.limiter_weno_lazy
 
     def Reconstruct(self):
         """mini::limiter::Reconstruct(part, limiter) (limiter/reconstruct.hpp:21-54): ShareGhostCellCoeffs, limit
@@ -87,13 +89,13 @@ class Spatial:
             return
         w0, eps = self._limiter
         if self.comm is None:
-            self.ctx.limiter_weno_lazy(w0, eps, -1)
+            self._limit_call(w0, eps, -1)
             return
         self.comm.drain()
         self.comm.start()                      # the unlimited values travel
-        self.ctx.limiter_weno_lazy(w0, eps, 0)
+        self._limit_call(w0, eps, 0)
         self.comm.finish()
-        self.ctx.limiter_weno_lazy(w0, eps, 1)
+        self._limit_call(w0, eps, 1)
 
     def SetDiffusion(self, beta_0, beta_1, nu, prandtl):
         """Riemann::Diffusion::SetBetaValues + SetProperty (direct.hpp:80-83, navier_stokes.hpp:57-60)."""

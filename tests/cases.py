@@ -126,3 +126,12 @@ def apply_viscous_spatial(sp, kinds=VISCOUS_BCS, vis=VISCOUS):
 # ---- weno::Lazy limiter -------------------------------------------------------------
 WENO = (0.001, 1e-6)                                   # demo/euler/sourceless.cpp:114
 WENO_GOLDEN_CASES = [("weno_p2_hllc", 2, 1), ("weno_p3_hllc", 3, 1)]   # (name, degree, riemann)
+WENO_EIGEN_GOLDEN_CASES = [("weno_eigen_p2_hllc", 2, 1), ("weno_eigen_p3_hllc", 3, 1)]
+
+
+def shocked_state(pts, seed=0, amp=1e-2, jump=3.0, x0=0.5):
+    """noisy_state with the whole state multiplied by `jump` beyond x = x0: some cells trip the detector of
+    weno::Eigen (limiter/weno.hpp:230-258), the others stay untouched."""
+    u = noisy_state(pts, seed=seed, amp=amp).reshape(pts.shape[:-1] + (5,)).copy()
+    u[pts[..., 0] > x0] *= jump
+    return u.reshape(-1)

@@ -77,7 +77,7 @@ def stage(mesh, degree, scheme, riemann, column_in, *, n_local=None, n_ghost=0, 
 
 
 def weno_lazy(mesh, degree, column_in, w0=0.001, eps=1e-6, *, n_local=None, n_ghost=0, cells=None, bfaces=None,
-              btags=None):
+              btags=None, eigen=False, global_ids=None):
     cells = np.ascontiguousarray(mesh.cells if cells is None else cells, dtype=np.int64)
     bfaces = np.ascontiguousarray(mesh.bfaces if bfaces is None else bfaces, dtype=np.int64)
     btags = np.ascontiguousarray(mesh.btags if btags is None else btags, dtype=np.int32)
@@ -92,7 +92,8 @@ def weno_lazy(mesh, degree, column_in, w0=0.001, eps=1e-6, *, n_local=None, n_gh
     rc = lib().emu_weno_lazy(C.c_int(degree), C.c_int64(len(nodes)), _dp(nodes), C.c_int64(n_local), C.c_int64(n_ghost),
                              _ip(cells), C.c_int64(len(bfaces)), _ip(bfaces), _i32(btags),
                              C.c_int64(0 if pairs is None else len(pairs)), _ip(pairs), C.c_double(w0), C.c_double(eps),
-                             _dp(column_in), _dp(out))
+                             _dp(column_in), _dp(out), C.c_int(1 if eigen else 0),
+                             None if global_ids is None else _ip(np.ascontiguousarray(global_ids, dtype=np.int64)))
     if rc != 0:
         raise RuntimeError("emu_weno_lazy failed")
     return out

@@ -58,6 +58,19 @@ def main():
         np.savez_compressed(os.path.join(HERE, name + ".npz"), u=u, limited=limited, u_rk3=u_rk3,
                             nodes=m.nodes, cells=m.cells, bfaces=m.bfaces, btags=m.btags)
         print(name, np.abs(limited - u).max())
+    # WithLimiter<fr::Lobatto, weno::Eigen>: detector + characteristic reconstruction, alone and inside RK3
+    for name, degree, riemann in cases.WENO_EIGEN_GOLDEN_CASES:
+        r = refapi.Ref(m, degree=degree, scheme=refapi.FR_WENO_EIGEN, riemann=riemann, weno=cases.WENO)
+        cases.apply_bcs_ref(r)
+        u = cases.shocked_state(cell_points(m.nodes, m.cells, degree))
+        r.set_solution_all(u)
+        limited = r.get_solution()
+        r.rk_update(3, 0.0, cases.GOLDEN_DT, 1)
+        u_rk3 = r.get_solution()
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), u=u, limited=limited, u_rk3=u_rk3,
+                            nodes=m.nodes, cells=m.cells, bfaces=m.bfaces, btags=m.btags)
+        kf = 5 * (degree + 1) ** 3
+        print(name, int((np.abs((limited - u).reshape(-1, kf)).max(1) > 0).sum()), "troubled cells of", m.n_cells)
 
 
 if __name__ == "__main__":

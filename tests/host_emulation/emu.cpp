@@ -108,7 +108,8 @@ int emu_stage(int degree, int scheme, int riemann, int64_t n_nodes, const double
 template <int Q>
 static void RunWeno(HostMesh const &mesh, std::vector<double> &u, std::vector<double> const &geom,
     std::vector<int> const &nbr, std::vector<unsigned char> const &code, std::vector<double> const &h2s,
-    std::vector<double> const &bas, int64_t first_inter, double w0, double eps) {
+    std::vector<double> const &bas, int64_t first_inter, double w0, double eps, bool eigen,
+    std::vector<double> const &frames) {
   constexpr int P = Q - 1, N = Q * Q * Q, F = 5 * N, M = ModalShape<P>::M, R = ModalShape<P>::kBasRows;
   const int64_t nl = mesh.n_local, nc = mesh.n_local + mesh.n_ghost, nt = (nc + kTile - 1) / kTile;
   std::vector<double> quad((size_t)nt * N * 4 * kTile, 0.0), mod((size_t)nt * 5 * M * kTile, 0.0), tay(mod), modn(mod), tayn(mod);
@@ -132,8 +133,40 @@ static void RunWeno(HostMesh const &mesh, std::vector<double> &u, std::vector<do
   WenoArgs a;
   a.u = u.data(); a.geom = geom.data(); a.bas = bas.data(); a.h2s = h2s.data(); a.nbr = nbr.data(); a.code = code.data();
   a.mod = mod.data(); a.tay = tay.data(); a.mod_new = modn.data(); a.tay_new = tayn.data(); a.w0 = w0; a.eps = eps;
+  std::vector<double> scratch((size_t)(7 * 5 * M + 5 * M) * kTile, 0.0);
+  auto limit_eigen_tile = [&](int64_t t) {   // WenoEigenKernel's phases, thread by thread
+    WenoEigenArgs e;
+    e.w = a; e.frames = frames.data(); e.cand = scratch.data(); e.blend = scratch.data() + (size_t)7 * 5 * M * kTile;
+    static EigenState<P> st[5][kTile];
+    auto q = [&](int l) { return quad.data() + t * N * 4 * kTile + l; };
+    auto bs = [&](int l) { return bas.data() + t * R * kTile + l; };
+    bool active[kTile];
+    for (int l = 0; l < kTile; ++l) {
+      const int64_t c = t * kTile + l;
+      active[l] = c >= a.cell_begin && c < a.cell_end;
+      for (int k = 0; k < 5; ++k) {
+        st[k][l].total_volume = 0; st[k][l].adj_cnt = 0; st[k][l].troubled = false;
+        for (int i = 0; i < M; ++i) st[k][l].total[i] = 0;
+        if (active[l]) st[k][l].troubled = WenoEigenDetect<Q>(a, (int)t, l, q(l), kTile, bs(l), kTile, &st[k][l].adj_cnt);
+        if (active[l] && st[k][l].troubled) WenoEigenBorrow<Q>(e, (int)t, l, k, q(l), kTile, bs(l), kTile);
+      }
+    }
+    for (int f = 0; f < 6; ++f) {
+      for (int l = 0; l < kTile; ++l) for (int k = 0; k < 5; ++k)
+        if (active[l] && st[k][l].troubled && nbr[(t * 6 + f) * kTile + l] >= 0)
+          WenoEigenFaceBlend<Q>(e, (int)t, l, k, f, st[k][l].adj_cnt, q(l), kTile, bs(l), kTile);
+      for (int l = 0; l < kTile; ++l) for (int k = 0; k < 5; ++k)
+        if (active[l] && st[k][l].troubled && nbr[(t * 6 + f) * kTile + l] >= 0)
+          WenoEigenFaceAccumulate<Q>(e, (int)t, l, k, f, bs(l), kTile, &st[k][l]);
+    }
+    for (int l = 0; l < kTile; ++l) for (int k = 0; k < 5; ++k)
+      if (active[l]) WenoEigenFinish<Q>(e, (int)t, l, k, q(l), kTile, bs(l), kTile, st[k][l]);
+  };
   auto limit = [&](int64_t b, int64_t e) {
     a.cell_begin = (int)b; a.cell_end = (int)e;
+    if (eigen) {
+      if (e > b) for (int64_t t = b / kTile; t <= (e - 1) / kTile; ++t) limit_eigen_tile(t);
+    } else
     for (int64_t c = b; c < e; ++c) for (int k = 0; k < 5; ++k) {
       const int64_t t = c >> 5; const int l = c & 31;
       WenoLazyCell<Q>(a, (int)t, l, k, quad.data() + t * N * 4 * kTile + l, kTile, bas.data() + t * R * kTile + l, kTile);
@@ -152,10 +185,12 @@ extern "C" {
 
 int emu_weno_lazy(int degree, int64_t n_nodes, const double *xyz, int64_t n_local, int64_t n_ghost,
     const int64_t *cell_nodes, int64_t n_bfaces, const int64_t *bface_nodes, const int32_t *bface_tags,
-    int64_t n_pairs, const int64_t *pairs, double w0, double eps, const double *column_in, double *column_out) {
+    int64_t n_pairs, const int64_t *pairs, double w0, double eps, const double *column_in, double *column_out,
+    int eigen, const int64_t *global_ids) {
   const int q = degree + 1, F = 5 * q * q * q;
   c_tab = BuildTables(degree, 0, (q == 3) ? kP2Warps : kP3Warps, kTile / ((q == 3) ? kP2Cells : kP3Cells));
   HostMesh mesh;
+  if (global_ids) mesh.global_ids.assign(global_ids, global_ids + n_local + n_ghost);
   if (!mesh.Build(degree, n_nodes, xyz, n_local, n_ghost, cell_nodes, n_bfaces, bface_nodes, bface_tags, n_pairs, pairs))
     return -1;
   const int64_t nc = n_local + n_ghost, nt = (nc + kTile - 1) / kTile;
@@ -170,8 +205,9 @@ int emu_weno_lazy(int degree, int64_t n_nodes, const double *xyz, int64_t n_loca
   int64_t first_inter = n_local;
   for (int64_t c = 0; c < n_local && first_inter == n_local; ++c)
     for (int f = 0; f < 6; ++f) if (mesh.nbr[c * 6 + f] >= n_local) { first_inter = c; break; }
-  if (q == 3) RunWeno<3>(mesh, u, geom, nbr, code, h2s, bas, first_inter, w0, eps);
-  else RunWeno<4>(mesh, u, geom, nbr, code, h2s, bas, first_inter, w0, eps);
+  auto frames = ToTiles(mesh.frames, 54, nc, nt);
+  if (q == 3) RunWeno<3>(mesh, u, geom, nbr, code, h2s, bas, first_inter, w0, eps, eigen != 0, frames);
+  else RunWeno<4>(mesh, u, geom, nbr, code, h2s, bas, first_inter, w0, eps, eigen != 0, frames);
   for (int64_t c = 0; c < n_local; ++c)
     for (int f = 0; f < F; ++f) column_out[c * F + f] = u[((c >> 5) * F + f) * kTile + (c & 31)];
   return 0;

@@ -173,3 +173,83 @@ def test_weno_two_parts_with_halo_buffers_match_the_reference_parts():
         t += 1e-3
     for k, sp in enumerate(S):
         assert relerr(sp.GetSolutionColumn(), r.get_solution(k)) < 1e-11
+
+
+# ---- weno::Eigen and EigenMatrices ------------------------------------------------------
+@pytest.mark.parametrize("name,degree,riemann", cases.WENO_EIGEN_GOLDEN_CASES)
+def test_weno_eigen_golden(name, degree, riemann):
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    m = meshmod.HexMesh(nodes=g["nodes"], cells=g["cells"], bfaces=g["bfaces"], btags=g["btags"])
+    sp = Spatial(Part(m), degree=degree, riemann=riemann, device=0)
+    cases.apply_bcs_spatial(sp, cases.MIXED_BCS)
+    sp.SetLimiter(*cases.WENO, eigen=True)
+    sp.SetSolutionColumn(g["u"])
+    got = sp.GetSolutionColumn()
+    kf = sp.kfields
+    touched = np.abs((g["limited"] - g["u"]).reshape(-1, kf)).max(1) > 0
+    assert np.array_equal(np.abs((got - g["u"]).reshape(-1, kf)).max(1) > 0, touched)   # same troubled cells
+    assert relerr(got, g["limited"]) < TOL
+    RungeKutta(3).Update(sp, 0.0, cases.GOLDEN_DT)
+    assert relerr(sp.GetSolutionColumn(), g["u_rk3"]) < 1e-11
+
+
+@pytest.mark.parametrize("degree", [2, 3])
+def test_weno_eigen_vs_oracle(degree):
+    m = meshmod.scramble(meshmod.box(4, 3, 3, warp=0.2, seed=4), seed=9)
+    u = cases.shocked_state(cell_points(m.nodes, m.cells, degree), seed=3)
+    o = oc.Oracle(m, degree, 0, 1)
+    sp = Spatial(Part(m), degree=degree, riemann=capi.HLLC, device=0)
+    sp.ctx.set_solution(u)
+    sp.ctx.limiter_weno_eigen(0.01, 1e-5)
+    assert relerr(sp.GetSolutionColumn(), o.weno_eigen(u, 0.01, 1e-5)) < TOL
+
+
+def test_eigen_matrices_on_device():
+    """mini::riemann::euler::EigenMatrices (eigen.hpp:27-56): L R = I, and both against the oracle."""
+    import ctypes as C
+    rng = np.random.default_rng(5)
+    n = 64
+    rho = rng.uniform(0.5, 2.0, n); vel = rng.uniform(-1, 1, (n, 3)); p = rng.uniform(0.5, 3.0, n)
+    cons = np.column_stack([rho, rho[:, None] * vel, p / 0.4 + 0.5 * rho * (vel ** 2).sum(1)])
+    q, _ = np.linalg.qr(rng.normal(size=(n, 3, 3)))
+    frames = np.ascontiguousarray(np.transpose(q, (0, 2, 1))).reshape(n, 9)    # rows = nu, mu, pi
+    sp = Spatial(Part(cases.small_mesh()), degree=2, riemann=capi.HLLC, device=0)
+    L, R = sp.ctx.eigen_matrices(cons, frames)
+    assert np.abs(L @ R - np.eye(5)).max() < 1e-12
+    lib = oc.lib()
+    for i in range(n):
+        Lo = np.empty(25); Ro = np.empty(25)
+        lib.oracle_eigen_matrices(oc._dp(np.ascontiguousarray(cons[i])), oc._dp(np.ascontiguousarray(frames[i])),
+                                  oc._dp(Lo), oc._dp(Ro))
+        assert np.abs(L[i].reshape(-1) - Lo).max() <= 1e-13 * np.abs(Lo).max()
+        assert np.abs(R[i].reshape(-1) - Ro).max() <= 1e-13 * np.abs(Ro).max()
+
+
+@pytest.mark.skipif(not refapi.available(2), reason="oracle/_ref not shipped")
+def test_weno_eigen_two_parts_match_the_reference_parts():
+    import torch
+    from minicfd_b200.halo import _DeviceArray
+    m = meshmod.scramble(meshmod.box(6, 4, 2, warp=0.1, seed=2), seed=3)
+    parts = (np.arange(m.n_cells) * 2 // m.n_cells).astype(np.int32)
+    u = cases.shocked_state(cell_points(m.nodes, m.cells, 2))
+    r = refapi.Ref(m, degree=2, scheme=refapi.FR_WENO_EIGEN, riemann=1, cell_parts=parts, n_parts=2, weno=cases.WENO)
+    P = [Part(m, parts, k, 2) for k in range(2)]
+    r.set_solution_all([p.gather_from_global(u, 135) for p in P])
+    S = [Spatial(p, degree=2, riemann=capi.HLLC, device=0) for p in P]
+    bufs = [sum(sp.ctx.halo_buffers(), ()) for sp in S]
+    for sp, p in zip(S, P):
+        sp.ctx.set_solution(p.gather_from_global(u, 135))
+    for sp in S:
+        sp.ctx.halo_pack()
+    torch.cuda.synchronize()
+    for a, b in ((0, 1), (1, 0)):
+        src = torch.as_tensor(_DeviceArray(bufs[a][0], bufs[a][1]), device="cuda")
+        dst = torch.as_tensor(_DeviceArray(bufs[b][2], bufs[b][3]), device="cuda")
+        dst.copy_(src)
+    torch.cuda.synchronize()
+    for sp in S:
+        sp.ctx.limiter_weno_eigen(*cases.WENO, 0)
+        sp.ctx.halo_unpack()
+        sp.ctx.limiter_weno_eigen(*cases.WENO, 1)
+    for k, sp in enumerate(S):
+        assert relerr(sp.GetSolutionColumn(), r.get_solution(k)) < TOL

