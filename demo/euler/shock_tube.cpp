@@ -49,7 +49,11 @@ using General = mini::spatial::fr::Lobatto<Part, Riemann>;
 #include "mini/limiter/weno.hpp"
 #include "mini/limiter/reconstruct.hpp"
 #include "mini/spatial/with_limiter.hpp"
+#ifdef EIGEN_LIMITER   // demo/euler/rotorcraft.hpp:41
+using Limiter = mini::limiter::weno::Eigen<Cell, Riemann>;
+#else
 using Limiter = mini::limiter::weno::Lazy<Cell>;
+#endif
 using Spatial = mini::spatial::WithLimiter<General, Limiter>;
 #else
 using Spatial = mini::spatial::fr::Lobatto<Part, Riemann>;
@@ -97,6 +101,11 @@ int main(int argc, char *argv[]) {
 #ifdef LIMITER   // demo/euler/sourceless.cpp:114-120
   auto limiter = Limiter(/* w0 = */0.001, /* eps = */1e-6);
   Spatial spatial(&limiter, &part);
+#ifdef EIGEN_LIMITER   // demo/euler/rotorcraft.cpp:93-96
+  using Face = typename Part::Face;
+  auto face_to_riemanns = [&spatial](Face const &face) -> auto const & { return spatial.GetRiemannSolvers(face); };
+  spatial.limiter_ptr()->InstallRiemannSolvers(face_to_riemanns);
+#endif
 #else
   Spatial spatial(&part);
 #endif

@@ -225,6 +225,7 @@ class Part {
     using Polynomial = Poly;
     using Scalar = typename Poly::Scalar;
   };
+  struct Face {};  // named by the lambda handed to weno::Eigen::InstallRiemannSolvers (demo/euler/rotorcraft.cpp:93-96)
 
   struct Halo {
     std::vector<int64_t> parts, send_counts, send_cells, recv_counts, recv_cells;
@@ -400,6 +401,11 @@ class FiniteElementB200 : public temporal::System<typename P::Scalar> {
 
   Part *part_ptr() const { return part_ptr_; }
   Part const &part() const { return *part_ptr_; }
+  // fem.hpp:113-116; the per-face solver objects do not exist on this side (nothing reads them)
+  std::vector<Riemann> const &GetRiemannSolvers(typename Part::Face const &) const {
+    static const std::vector<Riemann> none;
+    return none;
+  }
   mcfd_ctx *context() const { return ctx_; }
 
   template <class Callable>
@@ -509,7 +515,23 @@ template <typename Cell>
 class Lazy {
  public:
   using Scalar = typename Cell::Scalar;
+  static constexpr bool kEigen = false;
   Lazy(Scalar w0, Scalar eps, bool verbose = false) : w0_(w0), eps_(eps) { (void)verbose; }
+  Scalar w0() const { return w0_; }
+  Scalar eps() const { return eps_; }
+ private:
+  Scalar w0_, eps_;
+};
+// limiter/weno.hpp:197-349 -> mcfd_limiter_weno_eigen.  The face frames the reference takes from the installed
+// Riemann solvers (rotated::Euler::a/b/c of the face's first quadrature point) are derived from the mesh by the
+// library, so InstallRiemannSolvers has nothing left to do.
+template <typename Cell, typename Riemann>
+class Eigen {
+ public:
+  using Scalar = typename Cell::Scalar;
+  static constexpr bool kEigen = true;
+  Eigen(Scalar w0, Scalar eps) : w0_(w0), eps_(eps) {}
+  template <typename FaceToRiemann> void InstallRiemannSolvers(FaceToRiemann &&) {}
   Scalar w0() const { return w0_; }
   Scalar eps() const { return eps_; }
  private:
@@ -553,7 +575,11 @@ class WithLimiter : public ConcreteFiniteElement {
   void Reconstruct() {   // mini::limiter::Reconstruct(part_ptr, limiter_ptr), limiter/reconstruct.hpp:21-54
     if (!limiter_ptr_) return;
     mcfd_ctx *ctx = this->context();
-    b200::Check(mcfd_limiter_weno_lazy(ctx, limiter_ptr_->w0(), limiter_ptr_->eps(), -1), ctx, "mcfd_limiter_weno_lazy");
+    if constexpr (Limiter::kEigen) {
+      b200::Check(mcfd_limiter_weno_eigen(ctx, limiter_ptr_->w0(), limiter_ptr_->eps(), -1), ctx, "mcfd_limiter_weno_eigen");
+    } else {
+      b200::Check(mcfd_limiter_weno_lazy(ctx, limiter_ptr_->w0(), limiter_ptr_->eps(), -1), ctx, "mcfd_limiter_weno_lazy");
+    }
   }
   Limiter *limiter_ptr_;
 };

@@ -56,6 +56,7 @@ struct mcfd_ctx {
   DevBuf<double> bas, mod, tay, mod_new, tay_new;   // WENO limiter: per-cell bases and modal coefficients
   DevBuf<double> frames, weno_scratch;          // weno::Eigen: face frames, per-CTA candidate scratch
   std::vector<int64_t> global_ids;              // optional, for the next mcfd_set_mesh
+  cudaEvent_t trace_done = nullptr;             // local traces written (inner and inter stages may sit on different streams)
   int64_t first_inter = 0;                      // local cells [first_inter, n_local) have a ghost neighbour
   Viscosity vis{2.0, 1.0 / 12, 0.0, 0.0};       // Direct::SetBetaValues / NavierStokes::SetProperty
   double prandtl = 0.708;
@@ -330,6 +331,7 @@ int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
 int mcfd_destroy(mcfd_ctx *ctx) {
   if (!ctx) return MCFD_OK;
   for (auto &p : ctx->events) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
+  if (ctx->trace_done) cudaEventDestroy(ctx->trace_done);
   delete ctx;
   return MCFD_OK;
 }
@@ -664,6 +666,8 @@ int mcfd_rk_stage_inner(mcfd_ctx *ctx, int stage) {
   if (ctx->time_cb) ctx->time_cb(ctx->time_user, mcfd_rk_stage_time(ctx, stage));
   if (ctx->cfg.diffusion != MCFD_INVISCID) {   // the inner cells' neighbours are all local
     if (int s = LaunchTrace(ctx, ctx->u[in].p, 0, ctx->mesh.n_local)) return s;
+    if (!ctx->trace_done) MCFD_CUDA(ctx, cudaEventCreateWithFlags(&ctx->trace_done, cudaEventDisableTiming));
+    MCFD_CUDA(ctx, cudaEventRecord(ctx->trace_done, ctx->stream));
   }
   return LaunchStage(ctx, ctx->u[in].p, ctx->u[ctx->rk_u0].p, ctx->u[out].p, mode, ctx->rk_dt, 0,
       ctx->inner_blocks);
@@ -677,6 +681,8 @@ int mcfd_rk_stage_inter(mcfd_ctx *ctx, int stage) {
   StageBuffers(ctx, stage, &in, &out, &mode);
   if (in != ctx->rk_in) return Fail(ctx, MCFD_ERR_STATE, "stages must be run in order");
   if (ctx->cfg.diffusion != MCFD_INVISCID) {   // the ghost cells hold this stage's values by now
+    // the inter cells also read the local traces, which mcfd_rk_stage_inner may have launched on another stream
+    if (ctx->trace_done) MCFD_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->trace_done, 0));
     if (int s = LaunchTrace(ctx, ctx->u[in].p, ctx->mesh.n_local, ctx->n_cells)) return s;
   }
   if (int s = LaunchStage(ctx, ctx->u[in].p, ctx->u[ctx->rk_u0].p, ctx->u[out].p, mode, ctx->rk_dt,

@@ -25,24 +25,32 @@ def main():
     torch.cuda.set_device(local)
     os.environ.setdefault("TORCH_NCCL_HIGH_PRIORITY", "1"); dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     degree = int(sys.argv[1]) if len(sys.argv) > 1 else 2
+    mode = sys.argv[2] if len(sys.argv) > 2 else "euler"     # euler | viscous | weno
     px, py, pz = meshmod.factor3(world)
     m = meshmod.box(4 * px, 4 * py, 3 * pz, warp=0.1, seed=3)
     parts = meshmod.block_partition(m, px, py, pz)
     part = Part(m, parts, rank, world)
     kf = 5 * (degree + 1) ** 3
     comm = halo.for_part(part, kf)
-    sp = Spatial(part, degree=degree, riemann=capi.HLLC, device=local, comm=comm)
-    for tag in range(6):
-        sp.SetInviscidWall(tag)
-    u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), seed=4, amp=1e-4)
+    sp = Spatial(part, degree=degree, riemann=capi.HLLC, device=local, comm=comm,
+                 diffusion=capi.NAVIER_STOKES_DDG if mode == "viscous" else capi.INVISCID)
+    if mode == "viscous":
+        cases.apply_viscous_spatial(sp)
+    else:
+        for tag in range(6):
+            sp.SetInviscidWall(tag)
+    if mode == "weno":
+        sp.SetLimiter(*cases.WENO)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), seed=4, amp=1e-2 if mode == "weno" else 1e-4)
     sp.SetSolutionColumn(part.gather_from_global(u, kf))
-    n_steps, t = 5, 0.0
+    n_steps, t = (3 if mode == "weno" else 5), 0.0
     dts = []
     for _ in range(n_steps):
         dt = sp.GetTimeStep(2e-3, 3)        # includes the all-reduce(MIN)
         RungeKutta(3).Update(sp, t, dt)
         dts.append(dt)
         t += dt
+    sp.SetTime(t)
     res_local = sp.GetResidualColumn()      # also exercises the blocking exchange path
     sol = torch.from_numpy(np.zeros(m.n_cells * kf))
     res = torch.from_numpy(np.zeros(m.n_cells * kf))
@@ -52,10 +60,37 @@ def main():
     dist.all_reduce(sol)
     dist.all_reduce(res)
     ok = True
-    if rank == 0:
-        o = oc.Oracle(m, degree, 0, 1)
-        for tag in range(6):
-            o.set_bc(tag, 0)
+    if rank == 0 and mode == "weno":
+        # the limited result depends on the partition (limiter/reconstruct.hpp:46-51): compare with the
+        # reference run on the same parts
+        import refapi
+        if refapi.available(degree):
+            r = refapi.Ref(m, degree=degree, scheme=refapi.FR_WENO_LAZY, riemann=1, cell_parts=parts, n_parts=world,
+                           weno=cases.WENO)
+            for tag in range(6):
+                r.set_bc(tag, refapi.WALL)
+            P = [Part(m, parts, k, world) for k in range(world)]
+            r.set_solution_all([p.gather_from_global(u, kf) for p in P])
+            tt = 0.0
+            for dt in dts:
+                assert abs(r.time_step(2e-3, 3) - dt) <= 1e-12 * dt
+                r.rk_update(3, tt, dt, 1)
+                tt += dt
+            ref = np.zeros(m.n_cells * kf)
+            for k, p in enumerate(P):
+                p.scatter_to_global(r.get_solution(k), kf, ref)
+            e_u = np.abs(sol.cpu().numpy() - ref).max() / np.abs(ref).max()
+            print(f"MGPU world={world} degree={degree} weno: solution rel err {e_u:.2e}")
+            ok = e_u < 1e-11
+        else:
+            print("MGPU weno: reference binary not shipped, nothing to compare with")
+    elif rank == 0:
+        o = oc.Oracle(m, degree, 3 if mode == "viscous" else 0, 1)
+        if mode == "viscous":
+            cases.apply_viscous_oracle(o)
+        else:
+            for tag in range(6):
+                o.set_bc(tag, 0)
         ref, tt = u.copy(), 0.0
         for dt in dts:
             assert abs(o.time_step(ref, 2e-3, 3) - dt) <= 1e-12 * dt

@@ -17,13 +17,14 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _sod_reference(riemann, n_steps, limiter=False):
+def _sod_reference(riemann, n_steps, limiter=False, eigen=False):
     """The same loop as the driver, on the CPU checker (reference binary when shipped, else the C port)."""
     m = meshmod.box(50, 2, 3, hi=(5.0, 0.2, 0.3))
     left = np.array([1.0, 0, 0, 0, 1.0 / 0.4]); right = np.array([0.125, 0, 0, 0, 0.1 / 0.4])
     dt_max = 0.2 / 200
     if refapi.available(2):
-        r = refapi.Ref(m, degree=2, scheme=refapi.FR_WENO_LAZY if limiter else refapi.FR, riemann=riemann)
+        scheme = (refapi.FR_WENO_EIGEN if eigen else refapi.FR_WENO_LAZY) if limiter else refapi.FR
+        r = refapi.Ref(m, degree=2, scheme=scheme, riemann=riemann)
         def ic(tag, xyz, t, out, user):
             v = left if xyz[0] < 2.5 else right
             for k in range(5):
@@ -48,8 +49,8 @@ def _sod_reference(riemann, n_steps, limiter=False):
     x = cell_points(m.nodes, m.cells, 2)[..., 0]
     u = np.where((x < 2.5)[..., None], left, right).reshape(-1)
     if limiter:
-        o.set_limiter(0.001, 1e-6)
-        u = o.weno_lazy(u, 0.001, 1e-6)
+        o.set_limiter(0.001, 1e-6, eigen=eigen)
+        u = o.weno_eigen(u, 0.001, 1e-6) if eigen else o.weno_lazy(u, 0.001, 1e-6)
     t = 0.0
     for _ in range(n_steps):
         dt = o.time_step(u, dt_max, 3)
@@ -80,12 +81,13 @@ def test_sod_driver_through_cpp_template_api(tmp_path, flag, riemann, tol):
     assert np.abs(got - ref).max() / np.abs(ref).max() < tol
 
 
-def test_sod_driver_with_weno_limiter_through_cpp_template_api(tmp_path):
+@pytest.mark.parametrize("eigen", [False, True])
+def test_sod_driver_with_weno_limiter_through_cpp_template_api(tmp_path, eigen):
     """-DLIMITER: Extrapolation<Hexahedron>, WithLimiter<fr::Lobatto, weno::Lazy<Cell>>(&limiter, &part) as
     demo/euler/sourceless.hpp:41-80 and sourceless.cpp:114-120 spell them; the limiter runs after Approximate and
     after every Runge-Kutta stage."""
     exe = tmp_path / "shock_tube_weno"
-    subprocess.check_call(["g++", "-DUSE_HLLC", "-DLIMITER", "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"),
+    subprocess.check_call(["g++", "-DUSE_HLLC", "-DLIMITER", *(["-DEIGEN_LIMITER"] if eigen else []), "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"),
                            os.path.join(ROOT, "demo", "euler", "shock_tube.cpp"), "-o", str(exe),
                            "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200",
                            "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")])
@@ -94,7 +96,7 @@ def test_sod_driver_with_weno_limiter_through_cpp_template_api(tmp_path):
     res = subprocess.run([str(exe), str(n_steps), str(out)], capture_output=True, text=True, timeout=300)
     assert res.returncode == 0, res.stdout + res.stderr
     got = np.fromfile(out, dtype=np.float64)
-    ref = _sod_reference(1, n_steps, limiter=True)
+    ref = _sod_reference(1, n_steps, limiter=True, eigen=eigen)
     plain = _sod_reference(1, n_steps)
     assert np.abs(ref - plain).max() > 1e-3          # the limiter matters on a shock tube
     assert np.abs(got - ref).max() / np.abs(ref).max() < 1e-11
