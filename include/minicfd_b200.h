@@ -67,7 +67,11 @@ typedef enum {
  * rotated::Euler<..>, diffusive::Direct<diffusive::NavierStokes<Gas>>> as composed in
  * demo/laminar/shockless.hpp:43-57 (include/mini/riemann/concept.hpp:93-121, diffusive/navier_stokes.hpp,
  * diffusive/direct.hpp), on expansions with kLocal == false. */
-typedef enum { MCFD_INVISCID = 0, MCFD_NAVIER_STOKES_DDG = 1 } mcfd_diffusion;
+/* MCFD_CELL_VISCOSITY_DDG = ConvectionDiffusion<rotated::Euler<..>, diffusive::Direct<diffusive::Isotropic<Scalar, 5>>>
+ * (include/mini/riemann/diffusive/linear.hpp:103-121; demo/euler/sourceless.hpp:88-93 composes it for the VISCOSITY
+ * build), generalised to one viscosity per component and cell, which is the flux EnergyBasedViscosity adds
+ * (include/mini/spatial/viscosity.hpp:68-71, 114-129): F_k -= nu_k grad u_k. */
+typedef enum { MCFD_INVISCID = 0, MCFD_NAVIER_STOKES_DDG = 1, MCFD_CELL_VISCOSITY_DDG = 2 } mcfd_diffusion;
 
 typedef struct {
   int32_t scheme;    /* mcfd_scheme */
@@ -162,6 +166,13 @@ int mcfd_set_time_callback(mcfd_ctx *ctx, mcfd_time_callback fn, void *user);
  * becomes fr/general.hpp:460-479 + navier_stokes.hpp:204-224, its boundary values being
  * (unused, wall velocity u v w, normal temperature gradient) as in demo/laminar/cavity.cpp:30-38. */
 int mcfd_set_diffusion(mcfd_ctx *ctx, double beta_0, double beta_1, double nu, double prandtl);
+/* MCFD_CELL_VISCOSITY_DDG contexts: mcfd_set_diffusion's nu is Isotropic::SetProperty(nu) (linear.hpp:118-120), one
+ * value for every cell and component (prandtl unused).  mcfd_set_cell_viscosity replaces
+ * EnergyBasedViscosity::properties_ (viscosity.hpp:57, 68-71, 564-566): nu [n_local + n_ghost][5], constant inside a
+ * cell; a face uses the mean of its two cells (fr/general.hpp:331-335).  The ghost cells' values are the caller's to
+ * exchange (viscosity.hpp:163-189).  The rule that CHOOSES the values (UpdateProperties, viscosity.hpp:556-572, with
+ * the damping matrices of :299-384) is not part of this library yet. */
+int mcfd_set_cell_viscosity(mcfd_ctx *ctx, int64_t n_cells, const double *nu);
 
 /* -- temporal::System interface (include/mini/temporal/ode.hpp:17-48) -------------------------- */
 

@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(HERE, "libminicfd_b200.so")
 
 FR_LOBATTO, DG_LOBATTO, FR_GENERAL = 0, 1, 2
 EXACT, HLLC, AUSM = 0, 1, 2
-INVISCID, NAVIER_STOKES_DDG = 0, 1
+INVISCID, NAVIER_STOKES_DDG, CELL_VISCOSITY_DDG = 0, 1, 2
 (BC_INVISCID_WALL, BC_SUPERSONIC_OUTLET, BC_SUPERSONIC_INLET, BC_SUBSONIC_INLET, BC_SUBSONIC_OUTLET,
  BC_SMART, BC_NO_SLIP_WALL) = range(7)
 
@@ -54,6 +54,7 @@ SYMBOLS = {
     "mcfd_get_boundary_points": (C.c_int, [_P, C.c_int32, _D]),
     "mcfd_set_boundary_values": (C.c_int, [_P, C.c_int32, _D]),
     "mcfd_set_diffusion": (C.c_int, [_P, C.c_double, C.c_double, C.c_double, C.c_double]),
+    "mcfd_set_cell_viscosity": (C.c_int, [_P, C.c_int64, _D]),
     "mcfd_set_time_callback": (C.c_int, [_P, TIME_CALLBACK, _P]),
     "mcfd_count_local_cells": (C.c_int64, [_P]),
     "mcfd_cell_data_size": (C.c_int64, [_P]),
@@ -152,6 +153,10 @@ class Context:
 
     def set_diffusion(self, beta_0, beta_1, nu, prandtl):
         self._check(self.lib.mcfd_set_diffusion(self.h, beta_0, beta_1, nu, prandtl))
+
+    def set_cell_viscosity(self, nu):
+        nu = np.ascontiguousarray(nu, dtype=np.float64).reshape(-1, 5)
+        self._check(self.lib.mcfd_set_cell_viscosity(self.h, len(nu), _dp(nu)))
 
     def _check(self, rc):
         if rc != 0:

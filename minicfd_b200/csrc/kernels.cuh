@@ -88,7 +88,15 @@ struct StageArgs {
   const double *grad;           // [tile][node*15 + x*5 + c][lane]  global gradient at every node
   const double *hn;             // [tile][point*15 + x*5 + c][lane] Hessian . own outward unit normal
   const double *h2s;            // [tile][face*3 + x][lane]         Face::HolderToSharer of my face f
+  const double *cell_nu;        // [tile][comp][lane] kDiffIsotropic: viscosity of every component, per cell
   Viscosity vis;
+};
+
+// diffusive part of the Riemann type, a template parameter of the stage kernel
+enum : int {
+  kDiffNone = 0,
+  kDiffNavierStokes = 1,   // diffusive::Direct<diffusive::NavierStokes<Gas>>
+  kDiffIsotropic = 2       // diffusive::Direct<diffusive::Isotropic<Scalar, 5>> / EnergyBasedViscosity: nu per component and cell
 };
 
 enum : int {
@@ -391,7 +399,7 @@ MCFD_HD void StagePrologue(const StageArgs &p, int tid, int bid, double *smem) {
 
 // ---- phase A: contravariant fluxes Fhat = F(u) J* at every node -> shared memory --------------
 // (fr/general.hpp:276-279; fem.hpp:392-395; types.hpp:322-333; polynomial/hexahedron.hpp:607-611)
-template <int Q, int CPB, int NW, bool kViscous = false>
+template <int Q, int CPB, int NW, int kViscous = kDiffNone>
 MCFD_HD void StagePhaseA(const StageArgs &p, int tid, int bid, double *smem,
     const SlotStates<Q, CPB, NW> &st, SlotResiduals<Q, CPB, NW> *res) {
   using G = StageGeometry<Q, CPB, NW>;
@@ -429,7 +437,14 @@ MCFD_HD void StagePhaseA(const StageArgs &p, int tid, int bid, double *smem,
 #pragma unroll
         for (int c = 0; c < 5; ++c) gr[x][c] = src[(x * 5 + c) * kTile];
       }
-      NsMinusFluxMatrix(p.vis, u, gr, fx);
+      if (kViscous == kDiffNavierStokes) {
+        NsMinusFluxMatrix(p.vis, u, gr, fx);
+      } else {
+        double nu[5];
+#pragma unroll
+        for (int c = 0; c < 5; ++c) nu[c] = p.cell_nu[((size_t)g.tile * 5 + c) * kTile + g.tl];
+        IsoMinusFluxMatrix(nu, gr, fx);
+      }
     }
     double *dst = g.sF + (size_t)n * 15 * CPB + g.lc;
 #pragma unroll
@@ -531,7 +546,7 @@ MCFD_HD void LoadPoint(const StageArgs &p, const StageGeometry<Q, CPB, NW> &g, i
   }
 }
 
-template <int Q, int kRiemann, int CPB, int NW, bool kGeneral, bool kViscous = false>
+template <int Q, int kRiemann, int CPB, int NW, bool kGeneral, int kViscous = kDiffNone>
 MCFD_HD void StagePhaseB2(const StageArgs &p, int tid, int bid, double *smem) {
   using G = StageGeometry<Q, CPB, NW>;
   G g(p, tid, bid, smem);
@@ -599,7 +614,16 @@ MCFD_HD void StagePhaseB2(const StageArgs &p, int tid, int bid, double *smem) {
               gc[x][c] = (go[r] + gn[r]) * 0.5 + (pen0 * o[x]) * (cur.v[c] - cur.u[c]) - pen1 * (ho[r] + hb[r]);
             }
           }
-          NsMinusFluxNormal(p.vis, uc, gc, hs * nx, hs * ny, hs * nz, fl);
+          if (kViscous == kDiffNavierStokes) {
+            NsMinusFluxNormal(p.vis, uc, gc, hs * nx, hs * ny, hs * nz, fl);
+          } else {   // property = (mine + neighbour's) / 2, fr/general.hpp:331-335
+            double nu[5];
+#pragma unroll
+            for (int c = 0; c < 5; ++c)
+              nu[c] = (p.cell_nu[((size_t)g.tile * 5 + c) * kTile + g.tl]
+                     + p.cell_nu[((size_t)(cur.nb >> 5) * 5 + c) * kTile + (cur.nb & 31)]) * 0.5;
+            IsoMinusFluxNormal(nu, gc, hs * nx, hs * ny, hs * nz, fl);
+          }
         }
         if (!holder) scale = -scale;
       } else {
@@ -621,7 +645,14 @@ MCFD_HD void StagePhaseB2(const StageArgs &p, int tid, int bid, double *smem) {
 #pragma unroll
             for (int c = 0; c < 5; ++c) gr[x][c] = go[(x * 5 + c) * kTile];
           }
-          NsMinusFluxNoSlip(p.vis, wall, cur.u, gr, inv * nx, inv * ny, inv * nz, p.vis.beta0 * Rcp(dh), fl);
+          if (kViscous == kDiffNavierStokes) {
+            NsMinusFluxNoSlip(p.vis, wall, cur.u, gr, inv * nx, inv * ny, inv * nz, p.vis.beta0 * Rcp(dh), fl);
+          } else {   // linear.hpp:85-91: the cell's own gradient, no penalty
+            double nu[5];
+#pragma unroll
+            for (int c = 0; c < 5; ++c) nu[c] = p.cell_nu[((size_t)g.tile * 5 + c) * kTile + g.tl];
+            IsoMinusFluxNormal(nu, gr, inv * nx, inv * ny, inv * nz, fl);
+          }
         } else if (kind == kBcNoSlip) {
           // no face term at all for inviscid systems (fem.hpp:382-383): cancel the node's own
           // face-flux term that phase B1 has already added, -coef_F * sgn * (F(u) . J*col_d) / det
@@ -717,7 +748,7 @@ MCFD_HD void StagePhaseC(const StageArgs &p, int tid, int bid, double *smem,
 // One CTA-sized block, all phases; `sync` is __syncthreads() on the device and a no-op marker on the
 // host, where RunStageBlockOnHost() below replays the phases thread by thread.
 #ifdef __CUDACC__
-template <int Q, int kRiemann, int CPB, int NW, bool kGeneral, bool kViscous = false>
+template <int Q, int kRiemann, int CPB, int NW, bool kGeneral, int kViscous = kDiffNone>
 __global__ void __launch_bounds__(NW * 32, (Q == 3 ? (kViscous ? MCFD_P2_VMINB : MCFD_P2_MINB) : 1))
 StageKernel(StageArgs p) {
   extern __shared__ double smem[];
@@ -741,7 +772,7 @@ StageKernel(StageArgs p) {
   StagePhaseC<Q, CPB, NW, kGeneral>(p, tid, bid, smem, su, su0, res);
 }
 #else
-template <int Q, int kRiemann, int CPB, int NW, bool kGeneral, bool kViscous = false>
+template <int Q, int kRiemann, int CPB, int NW, bool kGeneral, int kViscous = kDiffNone>
 void RunStageBlockOnHost(const StageArgs &p, int bid, double *smem) {
   constexpr int T = NW * 32;
   static SlotStates<Q, CPB, NW> su[T], su0[T];

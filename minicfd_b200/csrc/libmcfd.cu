@@ -53,6 +53,7 @@ struct mcfd_ctx {
   std::map<int32_t, int32_t> tag_kind;
   DevBuf<double> u[3], res, geom, bvals, length, column;
   DevBuf<double> grad, hn, h2s;                 // viscous traces (TraceKernel) and HolderToSharer vectors
+  DevBuf<double> cell_nu;                       // MCFD_CELL_VISCOSITY_DDG: [tile][comp][lane]
   DevBuf<double> bas, mod, tay, mod_new, tay_new;   // WENO limiter: per-cell bases and modal coefficients
   DevBuf<double> frames, weno_scratch;          // weno::Eigen: face frames, per-CTA candidate scratch
   std::vector<int64_t> global_ids;              // optional, for the next mcfd_set_mesh
@@ -116,7 +117,7 @@ cudaError_t EnsureTables(mcfd_ctx *ctx) {
       return Fail(ctx, MCFD_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
   } while (0)
 
-template <int Q, int R, int CPB, int NW, bool kGeneral, bool kViscous = false>
+template <int Q, int R, int CPB, int NW, bool kGeneral, int kViscous = kDiffNone>
 cudaError_t LaunchStageG(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
   size_t smem = StageGeometry<Q, CPB, NW>::kSharedBytes;
   auto kernel = StageKernel<Q, R, CPB, NW, kGeneral, kViscous>;
@@ -146,13 +147,18 @@ cudaError_t LaunchStageQ(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
   }
 }
 
+template <int Q, int CPB, int NW, int kDiff>
+cudaError_t LaunchStageDiffusive(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
+  switch (ctx->cfg.riemann) {
+  case MCFD_EXACT: return LaunchStageG<Q, kExact, CPB, NW, false, kDiff>(ctx, a, n_blocks);
+  case MCFD_HLLC: return LaunchStageG<Q, kHllc, CPB, NW, false, kDiff>(ctx, a, n_blocks);
+  default: return LaunchStageG<Q, kAusm, CPB, NW, false, kDiff>(ctx, a, n_blocks);
+  }
+}
 template <int Q, int CPB, int NW>
 cudaError_t LaunchStageViscous(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
-  switch (ctx->cfg.riemann) {
-  case MCFD_EXACT: return LaunchStageG<Q, kExact, CPB, NW, false, true>(ctx, a, n_blocks);
-  case MCFD_HLLC: return LaunchStageG<Q, kHllc, CPB, NW, false, true>(ctx, a, n_blocks);
-  default: return LaunchStageG<Q, kAusm, CPB, NW, false, true>(ctx, a, n_blocks);
-  }
+  return ctx->cfg.diffusion == MCFD_NAVIER_STOKES_DDG ? LaunchStageDiffusive<Q, CPB, NW, kDiffNavierStokes>(ctx, a, n_blocks)
+                                                      : LaunchStageDiffusive<Q, CPB, NW, kDiffIsotropic>(ctx, a, n_blocks);
 }
 
 // Viscous traces (gradient at the nodes, Hessian . normal at the face points) of cells
@@ -194,7 +200,7 @@ int LaunchStage(mcfd_ctx *ctx, const double *u_in, const double *u0, double *u_o
   a.n_local = (int)ctx->mesh.n_local;
   a.block_begin = (int)block_begin;
   a.mode = mode; a.dt = dt; a.dt_dev = ctx->rk_order ? ctx->rk_dt_dev : nullptr;
-  a.grad = ctx->grad.p; a.hn = ctx->hn.p; a.h2s = ctx->h2s.p; a.vis = ctx->vis;
+  a.grad = ctx->grad.p; a.hn = ctx->hn.p; a.h2s = ctx->h2s.p; a.vis = ctx->vis; a.cell_nu = ctx->cell_nu.p;
   int n_blocks = (int)(block_end - block_begin);
   MCFD_CUDA(ctx, EnsureTables(ctx));
   cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -300,7 +306,7 @@ int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
     return Fail(nullptr, MCFD_ERR_ARG, "unknown scheme");
   if (config->riemann < MCFD_EXACT || config->riemann > MCFD_AUSM)
     return Fail(nullptr, MCFD_ERR_ARG, "unknown Riemann solver");
-  if (config->diffusion != MCFD_INVISCID && config->diffusion != MCFD_NAVIER_STOKES_DDG)
+  if (config->diffusion < MCFD_INVISCID || config->diffusion > MCFD_CELL_VISCOSITY_DDG)
     return Fail(nullptr, MCFD_ERR_ARG, "unknown diffusion model");
   if (config->diffusion != MCFD_INVISCID && config->scheme != MCFD_FR_LOBATTO)
     return Fail(nullptr, MCFD_ERR_ARG, "the viscous path is built for MCFD_FR_LOBATTO only");
@@ -391,6 +397,11 @@ int mcfd_set_mesh(mcfd_ctx *ctx, int64_t n_nodes, const double *xyz, int64_t n_l
     MCFD_CUDA(ctx, ctx->hn.Alloc((size_t)ctx->n_tiles * 6 * ctx->q * ctx->q * 15 * kTile));
     MCFD_CUDA(ctx, cudaMemset(ctx->grad.p, 0, ctx->grad.n * sizeof(double)));
     MCFD_CUDA(ctx, cudaMemset(ctx->hn.p, 0, ctx->hn.n * sizeof(double)));
+    if (ctx->cfg.diffusion == MCFD_CELL_VISCOSITY_DDG) {   // starts uniform at the nu of mcfd_set_diffusion
+      std::vector<double> nu((size_t)ctx->n_tiles * 5 * kTile, ctx->vis.nu);
+      MCFD_CUDA(ctx, ctx->cell_nu.Alloc(nu.size()));
+      MCFD_CUDA(ctx, cudaMemcpy(ctx->cell_nu.p, nu.data(), nu.size() * sizeof(double), cudaMemcpyHostToDevice));
+    }
   }
   size_t nb = ctx->mesh.bound_faces.size();
   ctx->btag_of_face.resize(nb);
@@ -553,6 +564,24 @@ int mcfd_set_diffusion(mcfd_ctx *ctx, double beta_0, double beta_1, double nu, d
   ctx->vis.nu = nu;
   ctx->vis.cond = nu * (kGasR * kGammaOverGm1) / prandtl;   // nu * Cp / Pr (navier_stokes.hpp:76-79)
   ctx->prandtl = prandtl;
+  if (ctx->cfg.diffusion == MCFD_CELL_VISCOSITY_DDG && ctx->cell_nu.p) {   // Isotropic::SetProperty(nu): uniform
+    std::vector<double> v((size_t)ctx->n_tiles * 5 * kTile, nu);
+    MCFD_CUDA(ctx, cudaMemcpyAsync(ctx->cell_nu.p, v.data(), v.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  }
+  return MCFD_OK;
+}
+
+int mcfd_set_cell_viscosity(mcfd_ctx *ctx, int64_t n_cells, const double *nu) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (ctx->cfg.diffusion != MCFD_CELL_VISCOSITY_DDG)
+    return Fail(ctx, MCFD_ERR_STATE, "the context was not created with MCFD_CELL_VISCOSITY_DDG");
+  if (!nu || n_cells != ctx->n_cells) return Fail(ctx, MCFD_ERR_ARG, "need [n_local + n_ghost][5] values");
+  std::vector<double> rows((size_t)n_cells * 5);
+  std::copy(nu, nu + n_cells * 5, rows.begin());
+  auto tiles = ToTiles(rows, 5, ctx->n_cells, ctx->n_tiles);
+  MCFD_CUDA(ctx, cudaMemcpyAsync(ctx->cell_nu.p, tiles.data(), tiles.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return MCFD_OK;
 }
 

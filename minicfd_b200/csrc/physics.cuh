@@ -564,6 +564,21 @@ MCFD_HD void NsMinusFluxNoSlip(const Viscosity &vis, const double *wall, const d
   NsMinusFluxCore(vis, u[0], gv, nx, ny, nz, wall[1], wall[2], wall[3], wall[4], flux);
 }
 
+// ---- component-wise isotropic diffusion --------------------------------------------------------------
+// diffusive::Isotropic (riemann/diffusive/linear.hpp:66-92, 103-121) with one nu for everything, or the flux that
+// EnergyBasedViscosity adds with one nu per component and cell (spatial/viscosity.hpp:114-129): F_k -= nu_k grad u_k.
+MCFD_HD void IsoMinusFluxMatrix(const double *nu, const double (*g)[5], double (*fx)[5]) {
+#pragma unroll
+  for (int x = 0; x < 3; ++x) {
+#pragma unroll
+    for (int k = 0; k < 5; ++k) fx[x][k] -= nu[k] * g[x][k];
+  }
+}
+MCFD_HD void IsoMinusFluxNormal(const double *nu, const double (*g)[5], double nx, double ny, double nz, double *flux) {
+#pragma unroll
+  for (int k = 0; k < 5; ++k) flux[k] -= nu[k] * (nx * g[0][k] + ny * g[1][k] + nz * g[2][k]);
+}
+
 // ---- EigenMatrices (riemann/euler/eigen.hpp:27-56) -----------------------------------------------
 // Left / right eigenvector matrices of the Euler flux Jacobian of the conservative state `u` along the
 // frame (nu, mu, pi) = f[0..2], f[3..5], f[6..8].  Row k of L and row c of R are all a thread of the

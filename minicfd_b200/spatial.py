@@ -74,6 +74,10 @@ class Spatial:
         demo/laminar/cavity.cpp:30-38; ignored by inviscid systems (fr/general.hpp:455-459)."""
         self._set_bc(tag, capi.BC_NO_SLIP_WALL, func, time_dependent)
 
+    def SetCellViscosity(self, nu):
+        """EnergyBasedViscosity::properties_ (viscosity.hpp:57, 564-566): nu[n_local + n_ghost][5]."""
+        self.ctx.set_cell_viscosity(nu)
+
     def SetLimiter(self, w0=0.001, eps=1e-6, eigen=False):
         """Makes this object behave like `WithLimiter<General, limiter::weno::Lazy<Cell>>(&limiter, &part)` with
         `limiter(w0, eps)` (spatial/with_limiter.hpp:21-68, demo/euler/sourceless.cpp:114-120): the limiter runs

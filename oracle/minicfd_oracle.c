@@ -395,6 +395,8 @@ typedef struct {
   double d2[MAXQ][MAXQ];               /* d2[i][m] = l_m''(x_i) */
   double *jtgrad;   /* [cell][n][3][3][3] d(J^-T)/d(xi_a) = mat_after_grad_of_U_, hexahedron.hpp:233-236 */
   double *dist;     /* [face][q*q] normal . HolderToSharer, fem.hpp:83-85 */
+  double *cell_nu;  /* scheme 6: [cell][5] viscosity of every component, constant inside a cell: what
+                       EnergyBasedViscosity::GetPropertyOnCell returns (viscosity.hpp:68-71); null = uniform nu */
   int limited;      /* WithLimiter<.., weno::Lazy>(w0, eps): the limiter follows every SetSolutionColumn */
   double weno_w0, weno_eps;
   double c_next;                       /* fr::General only (fr/general.hpp:218-219) */
@@ -615,12 +617,21 @@ void *oracle_create(int degree, int scheme, int riemann, int64_t n_nodes, const 
 
 void oracle_destroy(void *h) {
   oracle_t *o = h;
-  free(o->jtgrad); free(o->dist); free(o->xyz); free(o->jstar); free(o->jinv); free(o->det); free(o->length); free(o->holder); free(o->sharer);
+  free(o->cell_nu); free(o->jtgrad); free(o->dist); free(o->xyz); free(o->jstar); free(o->jinv); free(o->det); free(o->length); free(o->holder); free(o->sharer);
   free(o->tag); free(o->h_node); free(o->s_node); free(o->h_dir); free(o->s_dir); free(o->h_scale);
   free(o->s_scale); free(o->frame); free(o->fweight); free(o->fxyz); free(o);
 }
 
 void oracle_set_vincent(void *h, double c_next) { ((oracle_t *)h)->c_next = c_next; }
+void oracle_set_cell_viscosity(void *h, const double *nu) { /* [n_cells][5], or null for the uniform value */
+  oracle_t *o = h;
+  free(o->cell_nu);
+  o->cell_nu = NULL;
+  if (nu) {
+    o->cell_nu = malloc(sizeof(double) * o->n_cells * 5);
+    memcpy(o->cell_nu, nu, sizeof(double) * o->n_cells * 5);
+  }
+}
 void oracle_set_viscous(void *h, double beta0, double beta1, double nu, double prandtl) {
   oracle_t *o = h;
   o->beta0 = beta0; o->beta1 = beta1; o->nu = nu; o->prandtl = prandtl;
@@ -774,6 +785,17 @@ static void ns_minus_flux_no_slip(const oracle_t *o, double *f, const double *wa
   for (int x = 0; x < 3; ++x) for (int k = 0; k < 3; ++k) gp[x][1 + k] += nrm[x] * pen[k];
   ns_minus_flux_core(o, f, c[0], gp, nrm, &wall[1], wall[4]);
 }
+/* component-wise isotropic diffusion (diffusive/linear.hpp:66-92 with nu.x = nu.y = nu.z, or
+   EnergyBasedViscosity::MinusViscousFlux, spatial/viscosity.hpp:114-129, with one nu per component) */
+static void iso_cell_nu(const oracle_t *o, int64_t c, double *nu) {
+  for (int k = 0; k < 5; ++k) nu[k] = o->cell_nu ? o->cell_nu[c * 5 + k] : o->nu;
+}
+static void iso_minus_flux_matrix(double F[5][3], const double *nu, const double gc[3][5]) {
+  for (int k = 0; k < 5; ++k) for (int x = 0; x < 3; ++x) F[k][x] -= nu[k] * gc[x][k];
+}
+static void iso_minus_flux_normal(double *f, const double *nu, const double gc[3][5], const double *nrm) {
+  for (int k = 0; k < 5; ++k) f[k] -= nu[k] * (nrm[0] * gc[0][k] + nrm[1] * gc[1][k] + nrm[2] * gc[2][k]);
+}
 /* Direct::GetCommonGradient with the Hessian penalty (direct.hpp:45-78, 85-90) */
 static void ddg_common_gradient(const oracle_t *o, double dist, const double *nrm, const double *ul, const double *ur,
     const double gl[3][5], const double gr[3][5], const double hl[6][5], const double hr[6][5], double gc[3][5]) {
@@ -799,10 +821,16 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
     for (int a = 0; a < n; ++a) {
       double F[5][3];
       flux_matrix(&u[(c * n + a) * K], F);
-      if (o->scheme == 3) { /* fem.hpp:397-404 */
+      if (o->scheme == 3 || o->scheme == 6) { /* fem.hpp:397-404 */
         double gc[3][5];
         global_gradient(o, u, c, a, gc);
-        ns_minus_flux_matrix(o, F, &u[(c * n + a) * K], gc);
+        if (o->scheme == 3) {
+          ns_minus_flux_matrix(o, F, &u[(c * n + a) * K], gc);
+        } else {
+          double nu[5];
+          iso_cell_nu(o, c, nu);
+          iso_minus_flux_matrix(F, nu, gc);
+        }
       }
       const double *js = &o->jstar[(c * n + a) * 9];
       double *fh = &fhat[(c * n + a) * 15];
@@ -847,14 +875,21 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
       if (cs >= 0) {
         int as = o->s_node[f * fq + p];
         flux_upwind(o->riemann, fr, uh, &u[(cs * n + as) * K], fu);
-        if (o->scheme == 3) { /* fr/general.hpp:316-350 */
+        if (o->scheme == 3 || o->scheme == 6) { /* fr/general.hpp:316-350 */
           const double *us = &u[(cs * n + as) * K];
           double gh_[3][5], gs_[3][5], hh[6][5], hs[6][5], gcm[3][5], ucm[5];
           global_gradient_hessian(o, u, ch, ah, gh_, hh);
           global_gradient_hessian(o, u, cs, as, gs_, hs);
           ddg_common_gradient(o, o->dist[f * fq + p], fr->a, uh, us, gh_, gs_, hh, hs, gcm);
           for (int k = 0; k < 5; ++k) ucm[k] = (uh[k] + us[k]) / 2;
-          ns_minus_flux_normal(o, fu, ucm, gcm, fr->a);
+          if (o->scheme == 3) {
+            ns_minus_flux_normal(o, fu, ucm, gcm, fr->a);
+          } else { /* property = (holder's + sharer's) / 2, fr/general.hpp:331-335 */
+            double nh[5], nsh[5];
+            iso_cell_nu(o, ch, nh); iso_cell_nu(o, cs, nsh);
+            for (int k = 0; k < 5; ++k) { nh[k] += nsh[k]; nh[k] *= 0.5; }
+            iso_minus_flux_normal(fu, nh, gcm, fr->a);
+          }
         }
         if (o->scheme == 2) { /* fr/general.hpp:296-315, 409-434: the whole node line is corrected */
           double sh = o->h_scale[f * fq + p], ss = o->s_scale[f * fq + p];
@@ -874,7 +909,7 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
               }
             }
           }
-        } else if (o->scheme == 0 || o->scheme == 3) { /* fr/general.hpp:296-315, fr/lobatto.hpp:232-251 */
+        } else if (o->scheme == 0 || o->scheme == 3 || o->scheme == 6) { /* fr/general.hpp:296-315, fr/lobatto.hpp:232-251 */
           double sh = o->h_scale[f * fq + p], ss = o->s_scale[f * fq + p];
           double gh = sh > 0 ? gp : -gp, gs = ss > 0 ? gp : -gp;
           const double *Fh = &fhat[(ch * n + ah) * 15], *Fs = &fhat[(cs * n + as) * 15];
@@ -897,11 +932,17 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
         if (kind >= 2) eval_field(o->field_kind[tag], o->field_prm[tag], &o->fxyz[(f * fq + p) * 3], t, given);
         if (kind == 6) { /* no-slip wall: fr/lobatto.hpp:301-319, fr/general.hpp:460-479; no term at all for
                             inviscid systems (fr/general.hpp:455-459) */
-          if (o->scheme != 3) continue;
+          if (o->scheme != 3 && o->scheme != 6) continue;
           double gh_[3][5];
           boundary_flux(o->riemann, 0, fr, uh, given, fu);
           global_gradient(o, u, ch, ah, gh_);
-          ns_minus_flux_no_slip(o, fu, given, uh, gh_, fr->a, o->beta0 / o->dist[f * fq + p]);
+          if (o->scheme == 3) {
+            ns_minus_flux_no_slip(o, fu, given, uh, gh_, fr->a, o->beta0 / o->dist[f * fq + p]);
+          } else { /* linear.hpp:85-91: the plain normal flux of the cell's own gradient */
+            double nu[5];
+            iso_cell_nu(o, ch, nu);
+            iso_minus_flux_normal(fu, nu, gh_, fr->a);
+          }
         } else {
           boundary_flux(o->riemann, kind, fr, uh, given, fu);
         }
@@ -916,7 +957,7 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
             for (int k = 0; k < 5; ++k)
               res[(ch * n + base + i * strd[d]) * K + k] -= (fu[k] * sh - Fh[k * 3 + d]) * gpr;
           }
-        } else if (o->scheme == 0 || o->scheme == 3) { /* fr/lobatto.hpp:278-428 */
+        } else if (o->scheme == 0 || o->scheme == 3 || o->scheme == 6) { /* fr/lobatto.hpp:278-428 */
           double sh = o->h_scale[f * fq + p], gh = sh > 0 ? gp : -gp;
           const double *Fh = &fhat[(ch * n + ah) * 15];
           for (int k = 0; k < 5; ++k) res[(ch * n + ah) * K + k] -= (fu[k] * sh - Fh[k * 3 + o->h_dir[f]]) * gh;
@@ -996,7 +1037,7 @@ double oracle_time_step(void *h, const double *u, double dt_guess, int rk_order)
   }
   double dt = cfl[rk_order][o->degree] * min_dt;
   if (dt_guess < dt) dt = dt_guess;
-  if (o->scheme == 0 || o->scheme == 3) { dt *= 2.0; if (dt_guess < dt) dt = dt_guess; }
+  if (o->scheme == 0 || o->scheme == 3 || o->scheme == 6) { dt *= 2.0; if (dt_guess < dt) dt = dt_guess; }
   return dt;
 }
 

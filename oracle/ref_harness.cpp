@@ -62,6 +62,7 @@ using Scalar = double;
 #include "mini/riemann/rotated/euler.hpp"
 #include "mini/riemann/concept.hpp"
 #include "mini/riemann/diffusive/direct.hpp"
+#include "mini/riemann/diffusive/linear.hpp"
 #include "mini/riemann/diffusive/navier_stokes.hpp"
 #include "mini/spatial/dg/lobatto.hpp"
 #include "mini/spatial/fr/lobatto.hpp"
@@ -737,6 +738,14 @@ using VExact = Viscous<mini::riemann::euler::Exact<Gas, 3>>;
 using VHllc = Viscous<mini::riemann::euler::HartenLaxLeerContact<Gas, 3>>;
 using VAusm = Viscous<mini::riemann::euler::AdvectionUpstreamSplittingMethod<Gas, 3>>;
 
+// Euler + constant isotropic diffusion of every component with the direct-DG face flux: the diffusive Riemann type
+// that EnergyBasedViscosity wraps (demo/euler/sourceless.hpp:88-93), here with one uniform nu
+using IsoDiffusion = mini::riemann::diffusive::Direct<mini::riemann::diffusive::Isotropic<Scalar, 5>>;
+template <class Unrotated>
+using IsoViscous = mini::riemann::ConvectionDiffusion<Rotated<Unrotated>, IsoDiffusion>;
+using IExact = IsoViscous<mini::riemann::euler::Exact<Gas, 3>>;
+using IHllc = IsoViscous<mini::riemann::euler::HartenLaxLeerContact<Gas, 3>>;
+
 // c_next of the next fr::General to be created (fr/general.hpp:218-219); set by ref_pN_set_vincent
 static double g_c_next = 0.0;
 
@@ -772,6 +781,11 @@ static SolverBase *Create(int scheme, int riemann, GlobalMesh &&mesh) {
     case 0: return new SolverImpl<sp::WithLimiter<sp::fr::Lobatto<ModalPart, RExact>, mini::limiter::weno::Eigen<Cell, RExact>>>(std::move(mesh));
     case 1: return new SolverImpl<sp::WithLimiter<sp::fr::Lobatto<ModalPart, RHllc>, mini::limiter::weno::Eigen<Cell, RHllc>>>(std::move(mesh));
     }
+  } else if (scheme == 6) {
+    switch (riemann) {
+    case 0: return new SolverImpl<sp::fr::Lobatto<Part, IExact>>(std::move(mesh));
+    case 1: return new SolverImpl<sp::fr::Lobatto<Part, IHllc>>(std::move(mesh));
+    }
   } else if (scheme == 3) {
     switch (riemann) {
     case 0: return new SolverImpl<sp::fr::Lobatto<Part, VExact>>(std::move(mesh));
@@ -805,6 +819,8 @@ void REF_FN(set_vincent)(double c_next) { oracle::g_c_next = c_next; }
 void REF_FN(set_viscous)(double beta_0, double beta_1, double nu, double prandtl) {
   oracle::Diffusion::SetBetaValues(beta_0, beta_1);
   oracle::Diffusion::SetProperty(nu, prandtl);
+  oracle::IsoDiffusion::SetBetaValues(beta_0, beta_1);   // linear.hpp:118-120
+  oracle::IsoDiffusion::SetProperty(nu);
 }
 
 void *REF_FN(create)(int scheme, int riemann, Int n_nodes, const double *xyz, Int n_cells,

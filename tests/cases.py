@@ -135,3 +135,16 @@ def shocked_state(pts, seed=0, amp=1e-2, jump=3.0, x0=0.5):
     u = noisy_state(pts, seed=seed, amp=amp).reshape(pts.shape[:-1] + (5,)).copy()
     u[pts[..., 0] > x0] *= jump
     return u.reshape(-1)
+
+
+# ---- component-wise isotropic diffusion / per-cell viscosity (the flux path of SURVEY row a24) ------------------
+ISO_GOLDEN_CASES = [("iso_p2_hllc", 2, 1), ("iso_p3_exact", 3, 0)]   # uniform nu: Direct<Isotropic<Scalar, 5>>
+ISO_VISCOUS = (2.0, 1.0 / 12, 0.03, 0.708)
+
+
+def cell_viscosities(n_cells, seed=1):
+    """A per-cell, per-component viscosity table with zeros in it, like EnergyBasedViscosity produces."""
+    rng = np.random.default_rng(seed)
+    nu = rng.uniform(0.0, 0.05, (n_cells, 5))
+    nu[rng.uniform(size=nu.shape) < 0.3] = 0.0
+    return nu

@@ -46,6 +46,17 @@ def main():
         np.savez_compressed(os.path.join(HERE, name + ".npz"), u=u, residual=res, dt=dt, u_rk3=u_rk3,
                             nodes=m.nodes, cells=m.cells, bfaces=m.bfaces, btags=m.btags)
         print(name, np.linalg.norm(res), dt)
+    # fr::Lobatto on ConvectionDiffusion<rotated::Euler<..>, Direct<Isotropic<Scalar, 5>>>, uniform nu
+    for name, degree, riemann in cases.ISO_GOLDEN_CASES:
+        r = refapi.Ref(m, degree=degree, scheme=refapi.FR_ISOTROPIC, riemann=riemann)
+        cases.apply_viscous_ref(r, vis=cases.ISO_VISCOUS)
+        u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), amp=1e-4)
+        r.set_solution(u)
+        res = r.residual(cases.GOLDEN_T)
+        r.rk_update(3, 0.0, cases.GOLDEN_DT, 1)
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), u=u, residual=res, u_rk3=r.get_solution(),
+                            nodes=m.nodes, cells=m.cells, bfaces=m.bfaces, btags=m.btags)
+        print(name, np.linalg.norm(res))
     # WithLimiter<fr::Lobatto, weno::Lazy>: the limiter's action on a column, and an RK3 step with it
     for name, degree, riemann in cases.WENO_GOLDEN_CASES:
         r = refapi.Ref(m, degree=degree, scheme=refapi.FR_WENO_LAZY, riemann=riemann, weno=cases.WENO)

@@ -20,7 +20,8 @@ void RunStage(StageArgs a, int n_blocks) {
   using G = StageGeometry<Q, CPB, NW>;
   std::vector<double> smem(G::kSharedBytes / sizeof(double) + 1);
   for (int b = 0; b < n_blocks; ++b) {
-    if (a.grad) RunStageBlockOnHost<Q, R, CPB, NW, false, true>(a, b, smem.data());
+    if (a.grad && a.cell_nu) RunStageBlockOnHost<Q, R, CPB, NW, false, kDiffIsotropic>(a, b, smem.data());
+    else if (a.grad) RunStageBlockOnHost<Q, R, CPB, NW, false, kDiffNavierStokes>(a, b, smem.data());
     else if (c_tab.general) RunStageBlockOnHost<Q, R, CPB, NW, true>(a, b, smem.data());
     else RunStageBlockOnHost<Q, R, CPB, NW, false>(a, b, smem.data());
   }
@@ -53,7 +54,8 @@ int emu_stage(int degree, int scheme, int riemann, int64_t n_nodes, const double
     const int64_t *bface_nodes, const int32_t *bface_tags, int64_t n_pairs, const int64_t *pairs,
     const int32_t *tag_kinds, const double *bvals, const double *column_in, const double *column_u0,
     int mode, double dt, double *column_out, char *err, int err_len, double c_next,
-    const double *viscous /* null, or beta0, beta1, nu, prandtl */) {
+    const double *viscous /* null, or beta0, beta1, nu, prandtl */,
+    const double *cell_nu /* null, or [n_cells][5]: the component-wise isotropic model */) {
   const int q = degree + 1, F = 5 * q * q * q;
   const int cpb = (q == 3) ? kP2Cells : kP3Cells, nw = (q == 3) ? kP2Warps : kP3Warps;
   c_tab = BuildTables(degree, scheme, nw, kTile / cpb, c_next);
@@ -80,8 +82,13 @@ int emu_stage(int degree, int scheme, int riemann, int64_t n_nodes, const double
   a.geom = geom.data(); a.nbr = nbr.data(); a.code = code.data();
   a.bkind = bkind.data(); a.bvals = bvals ? bvals : zero_vals.data();
   a.n_local = (int)n_local; a.block_begin = 0; a.mode = mode; a.dt = dt;
-  a.dt_dev = nullptr; a.grad = nullptr; a.hn = nullptr; a.h2s = nullptr;
-  std::vector<double> grad, hn, h2s;
+  a.dt_dev = nullptr; a.grad = nullptr; a.hn = nullptr; a.h2s = nullptr; a.cell_nu = nullptr;
+  std::vector<double> grad, hn, h2s, nu_tiles;
+  if (viscous && cell_nu) {
+    std::vector<double> rows(cell_nu, cell_nu + nc * 5);
+    nu_tiles = ToTiles(rows, 5, nc, nt);
+    a.cell_nu = nu_tiles.data();
+  }
   if (viscous) {
     const int N = q * q * q;
     grad.assign((size_t)nt * N * 15 * kTile, 0.0);

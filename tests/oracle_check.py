@@ -57,6 +57,12 @@ class Oracle:
     def set_viscous(self, beta0, beta1, nu, prandtl):
         lib().oracle_set_viscous(self.h, C.c_double(beta0), C.c_double(beta1), C.c_double(nu), C.c_double(prandtl))
 
+    def set_cell_viscosity(self, nu):
+        """scheme 6: one viscosity per cell and component ([n_cells][5]); None = the uniform set_viscous value"""
+        a = None if nu is None else np.ascontiguousarray(nu, dtype=np.float64).reshape(self.n_cells, 5)
+        self._nu_keep = a
+        lib().oracle_set_cell_viscosity(self.h, _dp(a))
+
     def set_bc(self, tag, bc_kind, field_kind=F_CONST, params=None):
         p = np.zeros(8)
         if params is not None:

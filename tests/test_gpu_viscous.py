@@ -159,3 +159,30 @@ def test_navier_stokes_two_parts_with_halo_buffers():
             sp.ctx.rk_stage_inter(stage)
     for sp, p in zip(S, P):
         assert relerr(sp.GetSolutionColumn().reshape(-1, 135), expect_u[p.local_global]) < TOL
+
+
+# ---- component-wise isotropic diffusion, one viscosity per cell and component (flux path of SURVEY row a24) ----
+@pytest.mark.parametrize("name,degree,riemann", cases.ISO_GOLDEN_CASES)
+def test_cell_viscosity_golden_and_table(name, degree, riemann):
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    m = meshmod.HexMesh(nodes=g["nodes"], cells=g["cells"], bfaces=g["bfaces"], btags=g["btags"])
+    sp = Spatial(Part(m), degree=degree, riemann=riemann, device=0, diffusion=capi.CELL_VISCOSITY_DDG)
+    cases.apply_viscous_spatial(sp, vis=cases.ISO_VISCOUS)      # Isotropic::SetProperty(nu): uniform
+    sp.SetSolutionColumn(g["u"])
+    sp.SetTime(cases.GOLDEN_T)
+    assert relerr(sp.GetResidualColumn(), g["residual"]) < TOL
+    RungeKutta(3).Update(sp, 0.0, cases.GOLDEN_DT)
+    assert relerr(sp.GetSolutionColumn(), g["u_rk3"]) < TOL
+    # EnergyBasedViscosity::properties_: a table with zeros in it
+    nu = cases.cell_viscosities(m.n_cells)
+    o = oc.Oracle(m, degree, 6, riemann)
+    cases.apply_viscous_oracle(o, vis=cases.ISO_VISCOUS)
+    o.set_cell_viscosity(nu)
+    sp.SetCellViscosity(nu)
+    sp.SetSolutionColumn(g["u"])
+    sp.SetTime(cases.GOLDEN_T)
+    assert relerr(sp.GetResidualColumn(), o.residual(g["u"], cases.GOLDEN_T)) < TOL
+    for order in (1, 2, 3):
+        sp.SetSolutionColumn(g["u"])
+        RungeKutta(order).Update(sp, 0.0, 1e-3)
+        assert relerr(sp.GetSolutionColumn(), o.rk_update(g["u"], order, 0.0, 1e-3)) < TOL

@@ -136,6 +136,26 @@ def test_weno_kernel_source_on_host_matches_golden(name, degree, riemann):
     assert relerr(emuapi.weno_lazy(m, degree, g["u"], *cases.WENO), g["limited"]) < 1e-12
 
 
+@pytest.mark.parametrize("name,degree,riemann", cases.ISO_GOLDEN_CASES)
+def test_cell_viscosity_kernel_source_on_host(name, degree, riemann):
+    """Uniform nu against the reference's vectors; a per-cell, per-component table against the C oracle."""
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    m = meshmod.HexMesh(nodes=g["nodes"], cells=g["cells"], bfaces=g["bfaces"], btags=g["btags"])
+    holder, hf, tags, pts = emuapi.boundary(m, degree)
+    bv = np.zeros(pts.shape[:2] + (5,))
+    for tag, kind in cases.VISCOUS_BCS.items():
+        sel = tags == tag
+        bv[sel] = cases.viscous_bc_function(kind)(pts[sel], cases.GOLDEN_T)
+    kw = dict(tag_kinds=cases.VISCOUS_BCS, bvals=bv, viscous=cases.ISO_VISCOUS)
+    uniform = np.full((m.n_cells, 5), cases.ISO_VISCOUS[2])
+    assert relerr(emuapi.stage(m, degree, 0, riemann, g["u"], cell_nu=uniform, **kw), g["residual"]) < 1e-12
+    nu = cases.cell_viscosities(m.n_cells)
+    o = oc.Oracle(m, degree, 6, riemann)
+    cases.apply_viscous_oracle(o, vis=cases.ISO_VISCOUS)
+    o.set_cell_viscosity(nu)
+    assert relerr(emuapi.stage(m, degree, 0, riemann, g["u"], cell_nu=nu, **kw), o.residual(g["u"], cases.GOLDEN_T)) < 1e-12
+
+
 @pytest.mark.parametrize("name,degree,riemann", cases.WENO_EIGEN_GOLDEN_CASES)
 def test_weno_eigen_kernel_source_on_host_matches_golden(name, degree, riemann):
     g = np.load(os.path.join(GOLDEN, name + ".npz"))

@@ -150,6 +150,18 @@ def test_c_oracle_weno_eigen_matches_reference(degree):
     assert relerr(o.weno_eigen(u, 0.01, 1e-5), r.get_solution()) < TOL
 
 
+@pytest.mark.parametrize("name,degree,riemann", cases.ISO_GOLDEN_CASES)
+def test_c_oracle_isotropic_diffusion_matches_golden(name, degree, riemann):
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    o = oc.Oracle(_golden_mesh(g), degree, 6, riemann)
+    cases.apply_viscous_oracle(o, vis=cases.ISO_VISCOUS)
+    assert relerr(o.residual(g["u"], cases.GOLDEN_T), g["residual"]) < TOL
+    assert relerr(o.rk_update(g["u"], 3, 0.0, cases.GOLDEN_DT), g["u_rk3"]) < TOL
+    # a per-cell table holding the uniform value everywhere is the same thing
+    o.set_cell_viscosity(np.full((len(g["cells"]), 5), cases.ISO_VISCOUS[2]))
+    assert relerr(o.residual(g["u"], cases.GOLDEN_T), g["residual"]) < TOL
+
+
 def _flux_1d(rho, u, p):
     """Flux of a 1-D primitive state (test/riemann/euler/exact.cpp:34-39)."""
     e = p / 0.4 + 0.5 * rho * u * u
