@@ -1431,6 +1431,119 @@ void oracle_weno_eigen(void *h, double w0, double eps, double *u) {
   free(basis); free(modal); free(fresh); free(volume); free(troubled); free(adj_cnt); free(adj); free(adj_face);
 }
 
+/* ---- EnergyBasedViscosity (spatial/viscosity.hpp) on a single part ------------------------------------------- */
+/* Scalar viscous residual (nu = 1, every neighbour and boundary side zero) of one cell for nodal values v[n]:
+   what GetCellResidual(nu = 1) - GetCellResidual(nu = 0) leaves of UpdateCellResidual (viscosity.hpp:251-289, 313-331)
+   in component 0: AddFluxDivergence + AddFluxToHolder / AddFluxToSharer (fr/lobatto.hpp:252-277,
+   fr/general.hpp:356-408) on the six faces, then 1/detJ (viscosity.hpp:320-328). */
+static void energy_probe_residual(const oracle_t *o, int64_t c, const double *v, double *res) {
+  int q = o->q, n = o->n, fq = q * q;
+  double *u = calloc((size_t)o->n_cells * n * 5, sizeof(double));   /* the probe lives in all 5 components */
+  for (int a = 0; a < n; ++a) for (int k = 0; k < 5; ++k) u[(c * n + a) * 5 + k] = v[a];
+  double *fhat = malloc(sizeof(double) * n * 3);
+  for (int a = 0; a < n; ++a) {
+    double g[3][5];
+    global_gradient(o, u, c, a, g);
+    const double *js = &o->jstar[(c * n + a) * 9];
+    for (int d = 0; d < 3; ++d) fhat[a * 3 + d] = -(g[0][0] * js[0 * 3 + d] + g[1][0] * js[1 * 3 + d] + g[2][0] * js[2 * 3 + d]);
+  }
+  for (int a = 0; a < n; ++a) {
+    res[a] = 0;
+    for (int b = 0; b < n; ++b) {
+      double lg[3];
+      basis_local_gradient(o, a, b, lg);
+      res[a] -= fhat[b * 3] * lg[0] + fhat[b * 3 + 1] * lg[1] + fhat[b * 3 + 2] * lg[2];
+    }
+  }
+  double gp = g_prime_right_at_one(o->degree);
+  for (int64_t f = 0; f < o->n_faces; ++f) {
+    int holder = o->holder[f] == c, sharer = o->sharer[f] == c;
+    if (!holder && !sharer) continue;
+    for (int p = 0; p < fq; ++p) {
+      const frame_t *fr = &o->frame[f * fq + p];
+      int node = holder ? o->h_node[f * fq + p] : o->s_node[f * fq + p];
+      int dir = holder ? o->h_dir[f] : o->s_dir[f];
+      double scale = holder ? o->h_scale[f * fq + p] : o->s_scale[f * fq + p];
+      double g[3][5], H[6][5], zero3[3][5] = {{0}}, zero6[6][5] = {{0}}, uz[5] = {0}, uc[5], gc[3][5];
+      global_gradient_hessian(o, u, c, node, g, H);
+      for (int k = 0; k < 5; ++k) uc[k] = v[node];
+      if (holder) ddg_common_gradient(o, o->dist[f * fq + p], fr->a, uc, uz, g, zero3, H, zero6, gc);
+      else ddg_common_gradient(o, o->dist[f * fq + p], fr->a, uz, uc, zero3, g, zero6, H, gc);
+      double f_up = -(fr->a[0] * gc[0][0] + fr->a[1] * gc[1][0] + fr->a[2] * gc[2][0]);   /* nu = 1 */
+      double f_side = (holder ? f_up * scale : f_up * (-scale)) - fhat[node * 3 + dir];
+      res[node] -= f_side * (scale > 0 ? gp : -gp);
+    }
+  }
+  for (int a = 0; a < n; ++a) res[a] /= o->det[c * n + a];
+  free(u); free(fhat);
+}
+/* EnergyBasedViscosity::BuildDampingMatrices (viscosity.hpp:299-384): d[cell][r][c] */
+void oracle_damping_matrices(void *h, double *d) {
+  oracle_t *o = h;
+  int n = o->n;
+  double *v = malloc(sizeof(double) * n), *r = malloc(sizeof(double) * n);
+  for (int64_t c = 0; c < o->n_cells; ++c)
+    for (int col = 0; col < n; ++col) {
+      for (int a = 0; a < n; ++a) v[a] = a == col;
+      energy_probe_residual(o, c, v, r);
+      for (int a = 0; a < n; ++a) d[(c * n + a) * n + col] = r[a] * global_weight(o, c, a);
+    }
+  free(v); free(r);
+}
+/* EnergyBasedViscosity::UpdateProperties (viscosity.hpp:556-572): IntegrateJumpOnFaces (:446-475) and
+   GetViscosityValues (:477-544).  nu[cell][5]; returns min_dt_ (viscosity.hpp:574-578). */
+double oracle_update_viscosity(void *h, const double *u, const double *damping, double time_scale, double *nu) {
+  oracle_t *o = h;
+  int q = o->q, n = o->n, fq = q * q, P = o->degree;
+  int64_t nc = o->n_cells;
+  double *jump = calloc(nc * 5, sizeof(double)), *volume = calloc(nc, sizeof(double));
+  for (int64_t c = 0; c < nc; ++c) for (int a = 0; a < n; ++a) volume[c] += global_weight(o, c, a);
+  for (int64_t f = 0; f < o->n_interior; ++f) {
+    int64_t ch = o->holder[f], cs = o->sharer[f];
+    double area = 0;
+    for (int p = 0; p < fq; ++p) area += o->fweight[f * fq + p];
+    double hh = volume[ch] / area, hs = volume[cs] / area;   /* mesh/part.hpp:123-124 */
+    for (int p = 0; p < fq; ++p)
+      for (int k = 0; k < 5; ++k) {
+        double j = u[(ch * n + o->h_node[f * fq + p]) * 5 + k] - u[(cs * n + o->s_node[f * fq + p]) * 5 + k];
+        j *= j;
+        jump[ch * 5 + k] += j * (o->fweight[f * fq + p] * hh);
+        jump[cs * 5 + k] += j * (o->fweight[f * fq + p] * hs);
+      }
+  }
+  static const double spatial_factor[7] = {1., 4., 10., 40., 28., 50., 90.};
+  double min_dt = 1e100;
+  for (int64_t c = 0; c < nc; ++c) {
+    double max_speed = 1e-5, ref[5] = {1e-5, 1e-5, 1e-5, 1e-5, 1e-5};
+    for (int a = 0; a < n; ++a) { /* rotated/euler.hpp:340-355 */
+      const double *uc = &u[(c * n + a) * 5];
+      prim_t pr = cons_to_prim(uc);
+      double cs = sound_speed(pr.rho, pr.p), vel = sqrt(pr.u * pr.u + pr.v * pr.v + pr.w * pr.w);
+      double lam = fmax(cs + vel, cs - vel);
+      double sq_mass = uc[0] * uc[0], sq[5] = {sq_mass, sq_mass * lam * lam, sq_mass * lam * lam, sq_mass * lam * lam, uc[4] * uc[4]};
+      max_speed = fmax(max_speed, lam);
+      for (int k = 0; k < 5; ++k) ref[k] = fmax(ref[k], sq[k]);
+    }
+    double len = o->length[c];
+    min_dt = fmin(min_dt, len / max_speed);
+    double max_visc = max_speed * len / P, time_base = len / max_speed, scale = pow(len, (P + 1) + 3);
+    for (int k = 0; k < 5; ++k) {
+      if (jump[c * 5 + k] < ref[k] * scale) { nu[c * 5 + k] = 0; continue; }
+      double rate = 0;
+      for (int r = 0; r < n; ++r) {
+        double du = 0;
+        for (int a = 0; a < n; ++a) du += damping[(c * n + r) * n + a] * u[(c * n + a) * 5 + k];
+        rate += u[(c * n + r) * 5 + k] * du;
+      }
+      rate = -rate;
+      nu[c * 5 + k] = fmin(max_visc, fmax(0.0, jump[c * 5 + k] / (rate * (time_base * time_scale))));
+      min_dt = fmin(min_dt, len / (max_speed + spatial_factor[P] * nu[c * 5 + k] / len));
+    }
+  }
+  free(jump); free(volume);
+  return min_dt;
+}
+
 /* one rotated Riemann problem (test hook) */
 void oracle_riemann_flux(int riemann, int bc_kind, const double *frame9, const double *ul, const double *ur,
     double *f) {

@@ -54,6 +54,11 @@ using Scalar = double;
 #include "mini/limiter/weno.hpp"
 #include "mini/polynomial/extrapolation.hpp"
 #include "mini/spatial/with_limiter.hpp"
+// spatial/viscosity.hpp names MPI_Request (its own buffers) without including an MPI header
+struct ompi_request_t;
+typedef ompi_request_t *MPI_Request;
+#include "mini/spatial/viscosity.hpp"
+#include "mini/spatial/with_viscosity.hpp"
 #include "mini/polynomial/hexahedron.hpp"
 #include "mini/riemann/euler/ausm.hpp"
 #include "mini/riemann/euler/exact.hpp"
@@ -442,6 +447,24 @@ class OraclePart {
     return faces | std::views::transform([](Face *p) -> Face const & { return *p; });
   }
 
+  // part.hpp:1217-1231, 1242-1271, 1288-1308 as EnergyBasedViscosity uses them for its per-cell properties.  Its
+  // state is class-static (one spatial object per process), so the emulated multi-part mode cannot host it: these
+  // only serve a single part, where nothing is sent.
+  void InitializeRequestsAndBuffers(Int n_scalar_per_cell, std::vector<MPI_Request> *requests_ptr,
+      std::vector<std::vector<Scalar>> *send_data_ptr, std::vector<std::vector<Scalar>> *recv_data_ptr) const {
+    (void)n_scalar_per_cell; (void)requests_ptr; (void)send_data_ptr; (void)recv_data_ptr;
+    if (size_ != 1) std::abort();
+  }
+  template <class M>
+  void ShareGhostCellData(std::vector<MPI_Request> *, std::vector<std::vector<Scalar>> *,
+      std::vector<std::vector<Scalar>> *, M &&) {
+    if (size_ != 1) std::abort();
+  }
+  template <class M>
+  void UpdateGhostCellData(std::vector<MPI_Request> *, std::vector<std::vector<Scalar>> *, M &&) {
+    if (size_ != 1) std::abort();
+  }
+
   // part.hpp:1242-1278: pack the coefficients of the cells each neighbour needs.
   void ShareGhostCellCoeffs() {
     for (auto &[p, cells] : send_cell_ptrs_) {
@@ -548,6 +571,8 @@ struct SolverBase {
   virtual void approximate(FieldSpec const &spec) = 0;
   virtual void set_solution(int r, const double *col) = 0;
   virtual void set_solution_all(const double *cols) = 0;
+  virtual int cell_viscosity(double *nu) const { (void)nu; return -1; }        // [n_local][5], scheme 7
+  virtual int damping_matrices(double *d) { (void)d; return -1; }              // [n_local][N][N], scheme 7; zeroes the solution
   virtual void get_solution(int r, double *col) const = 0;
   virtual void residual_all(double t) = 0;
   virtual void get_residual(int r, double *col) const = 0;
@@ -595,6 +620,8 @@ struct SolverImpl : SolverBase {
           limiters[r]->InstallRiemannSolvers(
               [sp](typename Part::Face const &face) -> auto const & { return sp->GetRiemannSolvers(face); });
         }
+      } else if constexpr (requires { typename Spatial::Riemann::Viscosity; }) {   // WithViscosity's constructor is variadic
+        spatials[r] = std::make_unique<Spatial>(parts[r].get());
       } else if constexpr (std::is_constructible_v<Spatial, Part *, Scalar>) {
         spatials[r] = std::make_unique<Spatial>(parts[r].get(), c_next);   // fr::General(part, c_next)
       } else {
@@ -706,6 +733,27 @@ struct SolverImpl : SolverBase {
       }
     }
   }
+  int cell_viscosity(double *nu) const override {
+    if constexpr (requires { typename Spatial::Riemann::Viscosity; }) {
+      using V = typename Spatial::Riemann::Viscosity;
+      for (Int c = 0; c < parts[0]->CountLocalCells(); ++c) {
+        auto const &p = V::GetPropertyOnCell(c, 0);
+        for (int k = 0; k < 5; ++k) *nu++ = p[k];
+      }
+      return 0;
+    }
+    return -1;
+  }
+  int damping_matrices(double *d) override {
+    if constexpr (requires { typename Spatial::Riemann::Viscosity; }) {
+      using V = typename Spatial::Riemann::Viscosity;
+      auto mats = V::BuildDampingMatrices();   // viscosity.hpp:299-384; leaves the cells zeroed
+      constexpr int N = Part::Cell::N;
+      for (auto const &m : mats) for (int r = 0; r < N; ++r) for (int c = 0; c < N; ++c) *d++ = m(r, c);
+      return 0;
+    }
+    return -1;
+  }
   // all parts at once: under a limiter SetSolutionColumn exchanges ghost cells (with_limiter.hpp:58-61,
   // limiter/reconstruct.hpp:47-51), which needs every part to take part
   void set_solution_all(const double *cols) override {
@@ -746,6 +794,12 @@ using IsoViscous = mini::riemann::ConvectionDiffusion<Rotated<Unrotated>, IsoDif
 using IExact = IsoViscous<mini::riemann::euler::Exact<Gas, 3>>;
 using IHllc = IsoViscous<mini::riemann::euler::HartenLaxLeerContact<Gas, 3>>;
 
+// Euler with the energy-based artificial viscosity (demo/euler/sourceless.hpp:82-103 under VISCOSITY)
+template <class Unrotated>
+using Energy = mini::spatial::EnergyBasedViscosity<Part, IsoViscous<Unrotated>>;
+using EExact = Energy<mini::riemann::euler::Exact<Gas, 3>>;
+using EHllc = Energy<mini::riemann::euler::HartenLaxLeerContact<Gas, 3>>;
+
 // c_next of the next fr::General to be created (fr/general.hpp:218-219); set by ref_pN_set_vincent
 static double g_c_next = 0.0;
 
@@ -780,6 +834,12 @@ static SolverBase *Create(int scheme, int riemann, GlobalMesh &&mesh) {
     switch (riemann) {
     case 0: return new SolverImpl<sp::WithLimiter<sp::fr::Lobatto<ModalPart, RExact>, mini::limiter::weno::Eigen<Cell, RExact>>>(std::move(mesh));
     case 1: return new SolverImpl<sp::WithLimiter<sp::fr::Lobatto<ModalPart, RHllc>, mini::limiter::weno::Eigen<Cell, RHllc>>>(std::move(mesh));
+    }
+  } else if (scheme == 7) {   // single part only: EnergyBasedViscosity keeps its state in class statics
+    if (mesh.n_parts != 1) return nullptr;
+    switch (riemann) {
+    case 0: return new SolverImpl<sp::WithViscosity<sp::fr::Lobatto<Part, EExact>>>(std::move(mesh));
+    case 1: return new SolverImpl<sp::WithViscosity<sp::fr::Lobatto<Part, EHllc>>>(std::move(mesh));
     }
   } else if (scheme == 6) {
     switch (riemann) {
@@ -877,6 +937,8 @@ void REF_FN(approximate)(void *h, int field_kind, const double *params, int n_pa
   s.user = user;
   static_cast<SolverBase *>(h)->approximate(s);
 }
+int REF_FN(cell_viscosity)(void *h, double *nu) { return static_cast<SolverBase *>(h)->cell_viscosity(nu); }
+int REF_FN(damping_matrices)(void *h, double *d) { return static_cast<SolverBase *>(h)->damping_matrices(d); }
 void REF_FN(set_weno)(double w0, double eps) { oracle::g_weno_w0 = w0; oracle::g_weno_eps = eps; }
 void REF_FN(set_solution_all)(void *h, const double *cols) { static_cast<SolverBase *>(h)->set_solution_all(cols); }
 void REF_FN(set_solution)(void *h, int r, const double *col) {

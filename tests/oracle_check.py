@@ -63,6 +63,23 @@ class Oracle:
         self._nu_keep = a
         lib().oracle_set_cell_viscosity(self.h, _dp(a))
 
+    def damping_matrices(self):
+        """EnergyBasedViscosity::BuildDampingMatrices: [n_cells][N][N] (uses the beta values of set_viscous)"""
+        n = self.kfields // 5
+        out = np.empty((self.n_cells, n, n))
+        lib().oracle_damping_matrices(self.h, _dp(out))
+        return out
+
+    def update_viscosity(self, u, damping, time_scale=1.0):
+        """EnergyBasedViscosity::UpdateProperties: (nu[n_cells][5], min_dt)"""
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        d = np.ascontiguousarray(damping, dtype=np.float64)
+        nu = np.empty((self.n_cells, 5))
+        f = lib().oracle_update_viscosity
+        f.restype = C.c_double
+        min_dt = f(self.h, _dp(u), _dp(d), C.c_double(time_scale), _dp(nu))
+        return nu, float(min_dt)
+
     def set_bc(self, tag, bc_kind, field_kind=F_CONST, params=None):
         p = np.zeros(8)
         if params is not None:

@@ -12,7 +12,7 @@ _libs: dict[int, C.CDLL] = {}
 
 CB = C.CFUNCTYPE(None, C.c_int, C.POINTER(C.c_double), C.c_double, C.POINTER(C.c_double), C.c_void_p)
 
-FR, DG, FR_GENERAL, FR_VISCOUS, FR_WENO_LAZY, FR_WENO_EIGEN, FR_ISOTROPIC = 0, 1, 2, 3, 4, 5, 6
+FR, DG, FR_GENERAL, FR_VISCOUS, FR_WENO_LAZY, FR_WENO_EIGEN, FR_ISOTROPIC, FR_ENERGY_VISCOSITY = 0, 1, 2, 3, 4, 5, 6, 7
 EXACT, HLLC, AUSM = 0, 1, 2
 # boundary kinds, order of fem.hpp:196-222 as used by ref_harness.cpp
 WALL, SUPERSONIC_OUTLET, SUPERSONIC_INLET, SUBSONIC_INLET, SUBSONIC_OUTLET, SMART, NO_SLIP = range(7)
@@ -42,7 +42,7 @@ def _i32(a):
 
 class Ref:
     def __init__(self, mesh, degree=2, scheme=FR, riemann=HLLC, cell_parts=None, n_parts=1, c_next=0.0,
-                 weno=(0.001, 1e-6)):
+                 weno=(0.001, 1e-6), viscous=None):
         if degree not in _libs:
             _libs[degree] = C.CDLL(lib_path(degree))
         self.lib = _libs[degree]
@@ -52,6 +52,8 @@ class Ref:
         self.kfields = 5 * self.n_nodes_per_cell
         self._f("set_vincent")(C.c_double(c_next))
         self._f("set_weno")(C.c_double(weno[0]), C.c_double(weno[1]))
+        if viscous is not None:   # class statics: EnergyBasedViscosity builds its damping matrices at construction
+            self.set_viscous(*viscous)
         f = self._f("create")
         f.restype = C.c_void_p
         nodes = np.ascontiguousarray(mesh.nodes, dtype=np.float64)
@@ -140,6 +142,19 @@ class Ref:
                                    if isinstance(cols, (list, tuple)) else cols, dtype=np.float64)
         assert col.size == sum(self.count_local(r) for r in range(self.n_parts)) * self.kfields
         self._f("set_solution_all")(self.h, _dp(col))
+
+    def cell_viscosity(self):
+        """EnergyBasedViscosity::properties_ of the local cells (scheme FR_ENERGY_VISCOSITY): [n_local][5]"""
+        out = np.empty((self.count_local(0), 5))
+        assert self._f("cell_viscosity")(self.h, _dp(out)) == 0
+        return out
+
+    def damping_matrices(self):
+        """EnergyBasedViscosity::BuildDampingMatrices(): [n_local][N][N]; leaves the solution zeroed"""
+        n = self.n_nodes_per_cell
+        out = np.empty((self.count_local(0), n, n))
+        assert self._f("damping_matrices")(self.h, _dp(out)) == 0
+        return out
 
     def get_solution(self, r=0):
         out = np.empty(self.count_local(r) * self.kfields)
