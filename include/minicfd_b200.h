@@ -173,6 +173,23 @@ int mcfd_set_diffusion(mcfd_ctx *ctx, double beta_0, double beta_1, double nu, d
  * exchange (viscosity.hpp:163-189).  The rule that CHOOSES the values (UpdateProperties, viscosity.hpp:556-572, with
  * the damping matrices of :299-384) is not part of this library yet. */
 int mcfd_set_cell_viscosity(mcfd_ctx *ctx, int64_t n_cells, const double *nu);
+int mcfd_get_cell_viscosity(mcfd_ctx *ctx, double *nu);   /* [n_local + n_ghost][5] */
+
+/* EnergyBasedViscosity (include/mini/spatial/viscosity.hpp) + WithViscosity (with_viscosity.hpp:20-73) on
+ * MCFD_CELL_VISCOSITY_DDG contexts without ghost cells (the reference keeps this state in class statics: one spatial
+ * object per process).
+ * mcfd_build_damping_matrices = EnergyBasedViscosity::Initialize / BuildDampingMatrices (viscosity.hpp:299-384,
+ * 549-554): per cell the N x N matrix of the viscous operator (nu = 1, zero on the far side of every face) applied to
+ * the unit nodal vectors, rows scaled by the quadrature weights; built from N probe launches of the trace and stage
+ * kernels with the beta values of mcfd_set_diffusion.  From then on mcfd_time_step[_device] is WithViscosity::
+ * GetTimeStep: CFL * min_dt_ of the last update (with_viscosity.hpp:67-71).
+ * mcfd_update_cell_viscosity = EnergyBasedViscosity::UpdateProperties (viscosity.hpp:556-572) on the state the next
+ * residual reads: face-jump integrals (IntegrateJumpOnFaces, :446-475), then per cell and component
+ * nu = clamp(jump / (-u^T D u * h / lambda_max * time_scale)) or 0 below the reference value (GetViscosityValues,
+ * :477-544).  WithViscosity calls it after every SetSolutionColumn (with_viscosity.hpp:52-55). */
+int mcfd_build_damping_matrices(mcfd_ctx *ctx);
+int mcfd_get_damping_matrices(mcfd_ctx *ctx, double *matrices);   /* [n_local][N][N], row-major */
+int mcfd_update_cell_viscosity(mcfd_ctx *ctx, double time_scale);
 
 /* -- temporal::System interface (include/mini/temporal/ode.hpp:17-48) -------------------------- */
 

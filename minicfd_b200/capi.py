@@ -55,6 +55,10 @@ SYMBOLS = {
     "mcfd_set_boundary_values": (C.c_int, [_P, C.c_int32, _D]),
     "mcfd_set_diffusion": (C.c_int, [_P, C.c_double, C.c_double, C.c_double, C.c_double]),
     "mcfd_set_cell_viscosity": (C.c_int, [_P, C.c_int64, _D]),
+    "mcfd_get_cell_viscosity": (C.c_int, [_P, _D]),
+    "mcfd_build_damping_matrices": (C.c_int, [_P]),
+    "mcfd_get_damping_matrices": (C.c_int, [_P, _D]),
+    "mcfd_update_cell_viscosity": (C.c_int, [_P, C.c_double]),
     "mcfd_set_time_callback": (C.c_int, [_P, TIME_CALLBACK, _P]),
     "mcfd_count_local_cells": (C.c_int64, [_P]),
     "mcfd_cell_data_size": (C.c_int64, [_P]),
@@ -153,6 +157,23 @@ class Context:
 
     def set_diffusion(self, beta_0, beta_1, nu, prandtl):
         self._check(self.lib.mcfd_set_diffusion(self.h, beta_0, beta_1, nu, prandtl))
+
+    def build_damping_matrices(self):
+        self._check(self.lib.mcfd_build_damping_matrices(self.h))
+
+    def damping_matrices(self):
+        n = self.q ** 3
+        out = np.empty((self.n_local, n, n))
+        self._check(self.lib.mcfd_get_damping_matrices(self.h, _dp(out)))
+        return out
+
+    def update_cell_viscosity(self, time_scale=1.0):
+        self._check(self.lib.mcfd_update_cell_viscosity(self.h, time_scale))
+
+    def cell_viscosity(self, n_cells=None):
+        out = np.empty((self.n_local if n_cells is None else n_cells, 5))
+        self._check(self.lib.mcfd_get_cell_viscosity(self.h, _dp(out)))
+        return out
 
     def set_cell_viscosity(self, nu):
         nu = np.ascontiguousarray(nu, dtype=np.float64).reshape(-1, 5)

@@ -96,7 +96,10 @@ struct StageArgs {
 enum : int {
   kDiffNone = 0,
   kDiffNavierStokes = 1,   // diffusive::Direct<diffusive::NavierStokes<Gas>>
-  kDiffIsotropic = 2       // diffusive::Direct<diffusive::Isotropic<Scalar, 5>> / EnergyBasedViscosity: nu per component and cell
+  kDiffIsotropic = 2,      // diffusive::Direct<diffusive::Isotropic<Scalar, 5>> / EnergyBasedViscosity: nu per component and cell
+  // EnergyBasedViscosity::BuildDampingMatrices (spatial/viscosity.hpp:299-384): the viscous operator alone, nu = 1,
+  // every neighbour and every boundary side zero (AddFluxToHolder / AddFluxToSharer, fr/general.hpp:356-408)
+  kDiffProbe = 3
 };
 
 enum : int {
@@ -104,7 +107,8 @@ enum : int {
   kModeEuler = 1,     // out = u + R*dt                        (ode.hpp:121-133)
   kModeRk3b = 2,      // out = (u0*3 + (u + R*dt)) / 4         (rk.hpp:36-40)
   kModeRk3c = 3,      // out = ((u + R*dt)*2 + u0) / 3         (rk.hpp:42-47)
-  kModeRk2b = 4       // out = ((u + R*dt) + u0) * 0.5         (rk.hpp:24-29)
+  kModeRk2b = 4,      // out = ((u + R*dt) + u0) * 0.5         (rk.hpp:24-29)
+  kModeProbe = 5      // host-side only: a residual with the kDiffProbe instantiation (damping matrices)
 };
 
 MCFD_CONSTANT Tables c_tab;
@@ -439,6 +443,14 @@ MCFD_HD void StagePhaseA(const StageArgs &p, int tid, int bid, double *smem,
       }
       if (kViscous == kDiffNavierStokes) {
         NsMinusFluxMatrix(p.vis, u, gr, fx);
+      } else if (kViscous == kDiffProbe) {
+        const double one[5] = {1, 1, 1, 1, 1};
+#pragma unroll
+        for (int x = 0; x < 3; ++x) {
+#pragma unroll
+          for (int c = 0; c < 5; ++c) fx[x][c] = 0;
+        }
+        IsoMinusFluxMatrix(one, gr, fx);
       } else {
         double nu[5];
 #pragma unroll
@@ -572,7 +584,32 @@ MCFD_HD void StagePhaseB2(const StageArgs &p, int tid, int bid, double *smem) {
       double fl[5];
       // lumped: the lifted term itself; general: |n| f* along my outward normal, lifted in phase C
       double scale = kGeneral ? area : -c_tab.coef_f * area;
-      if (cur.nb >= 0) {
+      if (kViscous == kDiffProbe) {
+        // zero on the other side of EVERY face, boundary ones included; no Riemann flux; nu = 1
+        const bool holder = (cur.code & 64) != 0;
+        const double hs = (holder ? sgn : -sgn) * inv_area;
+        const double os_ = sgn * inv_area;
+        const double o[3] = {os_ * nx, os_ * ny, os_ * nz};
+        const double *hv = p.h2s + ((size_t)g.tile * 18 + f * 3) * kTile + g.tl;
+        const double dh = (hs * nx) * hv[0] + (hs * ny) * hv[kTile] + (hs * nz) * hv[2 * kTile];
+        const double pen0 = p.vis.beta0 * Rcp(dh), pen1 = p.vis.beta1 * dh;
+        const double *go = p.grad + ((size_t)g.tile * G::N * 15 + n * 15) * kTile + g.tl;
+        const double *ho = p.hn + ((size_t)g.tile * G::POINTS * 15 + pt * 15) * kTile + g.tl;
+        double gc[3][5];
+#pragma unroll
+        for (int x = 0; x < 3; ++x) {
+#pragma unroll
+          for (int c = 0; c < 5; ++c) {
+            const int r = (x * 5 + c) * kTile;
+            gc[x][c] = go[r] * 0.5 - (pen0 * o[x]) * cur.u[c] - pen1 * ho[r];
+          }
+        }
+        const double one[5] = {1, 1, 1, 1, 1};
+#pragma unroll
+        for (int c = 0; c < 5; ++c) fl[c] = 0;
+        IsoMinusFluxNormal(one, gc, hs * nx, hs * ny, hs * nz, fl);
+        if (!holder) scale = -scale;
+      } else if (cur.nb >= 0) {
         // The Riemann problem is posed in the holder's frame, as the reference does: when the
         // neighbour holds the face, swap the states, flip the normal and negate the result.
         const bool holder = (cur.code & 64) != 0;
@@ -1293,6 +1330,118 @@ __global__ void CopyCellRowsKernel(const double *src, double *dst, int rows, int
   if (cell >= cell_end) return;
   const size_t base = (size_t)(cell >> 5) * rows * kTile + (cell & 31);
   for (int r = 0; r < rows; ++r) dst[base + (size_t)r * kTile] = src[base + (size_t)r * kTile];
+}
+#endif
+
+// ---- EnergyBasedViscosity::UpdateProperties (spatial/viscosity.hpp:556-572) --------------------------------
+// One (cell, component): the jump integral over the cell's interior faces (IntegrateJumpOnFaces, :446-475; the
+// face weight is w_a w_b |J* column| from the cell's own metric, the height volume / area), the reference square
+// and speed (rotated/euler.hpp:340-355), the damping rate -u^T D u and the clamped viscosity (:477-544).
+// Returns this thread's contribution to min_dt_.  D: [tile][r*N + c][lane], nu out: [tile][comp][lane].
+template <int Q>
+MCFD_HD double ViscosityCell(const double *u, const double *geom, const int *nbr, const unsigned char *code,
+    const unsigned char *nbr_node, const double *damping, const double *length, int tile, int tl, int comp,
+    double time_scale, double *nu_out) {
+  constexpr int P = Q - 1, N = Q * Q * Q, F = 5 * N, FQ = Q * Q;
+  const double *mine = u + (size_t)tile * F * kTile + tl;
+  const double *geo = geom + (size_t)tile * kGeomRows * kTile + tl;
+  double volume = 0;
+  for (int n = 0; n < N; ++n) {
+    double d[3], w;
+    QuadraturePoint<Q>(n, geo, kTile, d, &w);
+    volume += w;
+  }
+  double jump = 0;
+  for (int f = 0; f < 6; ++f) {
+    const int nb = nbr[((size_t)tile * 6 + f) * kTile + tl];
+    if (nb < 0) continue;
+    const int cd = code[((size_t)tile * 6 + f) * kTile + tl];
+    const int dir = (f == 2 || f == 4) ? 0 : ((f == 1 || f == 3) ? 1 : 2);
+    double area = 0, sum = 0;
+    for (int q = 0; q < FQ; ++q) {
+      const int n = c_tab.face_node[f][q];
+      const int i = n / FQ, j = (n / Q) % Q, k = n % Q;
+      double nrm[3];
+      ComputeNormal(geo, kTile, c_tab.xi[i], c_tab.xi[j], c_tab.xi[k], dir, nrm);
+      const int ia = dir == 0 ? j : i, ib = dir == 2 ? j : k;     // the two in-face indices
+      const double w = c_tab.w[ia] * c_tab.w[ib] * Sqrt(nrm[0] * nrm[0] + nrm[1] * nrm[1] + nrm[2] * nrm[2]);
+      const int n2 = nbr_node[((cd & 7) * 8 + ((cd >> 3) & 7)) * FQ + q];
+      const double v = u[((size_t)(nb >> 5) * F + n2 * 5 + comp) * kTile + (nb & 31)];
+      const double dj = mine[(size_t)(n * 5 + comp) * kTile] - v;
+      area += w;
+      sum = fma(dj * dj, w, sum);
+    }
+    jump = fma(sum, volume / area, jump);
+  }
+  double max_speed = 1e-5, ref = 1e-5;
+  for (int n = 0; n < N; ++n) {
+    const double *s = mine + (size_t)n * 5 * kTile;
+    const double r0 = s[0], r4 = s[4 * kTile];
+    const Prim pr = ConsToPrim(r0, s[kTile], s[2 * kTile], s[3 * kTile], r4);
+    const double cs = SoundSpeed(pr.rho, pr.p), vel = Sqrt(pr.u * pr.u + pr.v * pr.v + pr.w * pr.w + 1e-300);
+    const double lam = fmax(cs + vel, cs - vel);
+    max_speed = fmax(max_speed, lam);
+    const double sq = comp == 0 ? r0 * r0 : (comp == 4 ? r4 * r4 : r0 * r0 * lam * lam);
+    ref = fmax(ref, sq);
+  }
+  const double len = length[(size_t)tile * kTile + tl];
+  double min_dt = len / max_speed;
+  const double max_visc = max_speed * len / P, time_base = len / max_speed;
+  double scale = len * len * len * len * len * len;            // h^(P+1) * h^3, P = 2
+  if (P == 3) scale *= len;
+  double nu = 0;
+  if (!(jump < ref * scale)) {
+    const double *D = damping + (size_t)tile * N * N * kTile + tl;
+    double rate = 0;
+    for (int r = 0; r < N; ++r) {
+      double du = 0;
+      for (int c = 0; c < N; ++c) du = fma(D[(size_t)(r * N + c) * kTile], mine[(size_t)(c * 5 + comp) * kTile], du);
+      rate = fma(mine[(size_t)(r * 5 + comp) * kTile], du, rate);
+    }
+    rate = -rate;
+    nu = fmin(max_visc, fmax(0.0, jump / (rate * (time_base * time_scale))));
+    const double factor = P == 2 ? 10.0 : 40.0;                // GetSpatialFactor, viscosity.hpp:579-600
+    min_dt = fmin(min_dt, len / (max_speed + factor * nu / len));
+  }
+  nu_out[((size_t)tile * 5 + comp) * kTile + tl] = nu;
+  return min_dt;
+}
+
+#ifdef __CUDACC__
+template <int Q>
+__global__ void __launch_bounds__(160) ViscosityKernel(const double *u, const double *geom, const int *nbr,
+    const unsigned char *code, const double *damping, const double *length, int n_local, double time_scale,
+    double *nu_out, unsigned long long *min_dt_bits) {
+  __shared__ unsigned char sNbrNode[6 * 8 * Q * Q];
+  for (int i = threadIdx.x; i < 6 * 8 * Q * Q; i += 160) sNbrNode[i] = c_tab.nbr_node[i / (8 * Q * Q)][(i / (Q * Q)) % 8][i % (Q * Q)];
+  __syncthreads();
+  const int tile = blockIdx.x, lane = threadIdx.x & 31, comp = threadIdx.x >> 5;
+  double dt = 1e100;
+  if (tile * kTile + lane < n_local)
+    dt = ViscosityCell<Q>(u, geom, nbr, code, sNbrNode, damping, length, tile, lane, comp, time_scale, nu_out);
+  for (int o = 16; o > 0; o >>= 1) dt = fmin(dt, __shfl_xor_sync(0xffffffffu, dt, o));
+  if (lane == 0) atomicMin(min_dt_bits, (unsigned long long)__double_as_longlong(dt));
+}
+// column `col` of every cell's damping matrix from the probe residual (component 0), scaled by the row's
+// quadrature weight (viscosity.hpp:335-337, 371-382)
+template <int Q>
+__global__ void DampingColumnKernel(const double *res, const double *geom, double *damping, int col, int n_local) {
+  constexpr int N = Q * Q * Q, F = 5 * N;
+  const int cell = blockIdx.x * blockDim.x + threadIdx.x;
+  if (cell >= n_local) return;
+  const int tile = cell >> 5, tl = cell & 31;
+  for (int r = 0; r < N; ++r) {
+    double d[3], w;
+    QuadraturePoint<Q>(r, geom + (size_t)tile * kGeomRows * kTile + tl, kTile, d, &w);
+    damping[((size_t)tile * N * N + r * N + col) * kTile + tl] = res[((size_t)tile * F + r * 5) * kTile + tl] * w;
+  }
+}
+// every cell's nodal values := 1 at node `col`, 0 elsewhere, in all components (viscosity.hpp:341-346)
+__global__ void ProbeStateKernel(double *u, int rows_per_tile, int n_tiles, int col) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)n_tiles * rows_per_tile * kTile) return;
+  const int row = (int)((i / kTile) % rows_per_tile);
+  u[i] = (row / 5 == col) ? 1.0 : 0.0;
 }
 #endif
 

@@ -54,6 +54,9 @@ struct mcfd_ctx {
   DevBuf<double> u[3], res, geom, bvals, length, column;
   DevBuf<double> grad, hn, h2s;                 // viscous traces (TraceKernel) and HolderToSharer vectors
   DevBuf<double> cell_nu;                       // MCFD_CELL_VISCOSITY_DDG: [tile][comp][lane]
+  DevBuf<double> damping;                       // EnergyBasedViscosity: [tile][r*N + c][lane] damping matrices
+  DevBuf<unsigned long long> visc_dt_bits;      // min_dt_ of the last mcfd_update_cell_viscosity
+  bool energy_viscosity = false;                // WithViscosity mode: the time step comes from min_dt_
   DevBuf<double> bas, mod, tay, mod_new, tay_new;   // WENO limiter: per-cell bases and modal coefficients
   DevBuf<double> frames, weno_scratch;          // weno::Eigen: face frames, per-CTA candidate scratch
   std::vector<int64_t> global_ids;              // optional, for the next mcfd_set_mesh
@@ -157,6 +160,11 @@ cudaError_t LaunchStageDiffusive(mcfd_ctx *ctx, StageArgs const &a, int n_blocks
 }
 template <int Q, int CPB, int NW>
 cudaError_t LaunchStageViscous(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
+  if (a.mode == kModeProbe) {   // damping-matrix probes never solve a Riemann problem: one instantiation serves all
+    StageArgs b = a;
+    b.mode = kModeResidual;
+    return LaunchStageG<Q, kHllc, CPB, NW, false, kDiffProbe>(ctx, b, n_blocks);
+  }
   return ctx->cfg.diffusion == MCFD_NAVIER_STOKES_DDG ? LaunchStageDiffusive<Q, CPB, NW, kDiffNavierStokes>(ctx, a, n_blocks)
                                                       : LaunchStageDiffusive<Q, CPB, NW, kDiffIsotropic>(ctx, a, n_blocks);
 }
@@ -391,7 +399,7 @@ int mcfd_set_mesh(mcfd_ctx *ctx, int64_t n_nodes, const double *xyz, int64_t n_l
     MCFD_CUDA(ctx, ctx->h2s.Alloc(h2s.size()));
     MCFD_CUDA(ctx, cudaMemcpy(ctx->h2s.p, h2s.data(), h2s.size() * sizeof(double), cudaMemcpyHostToDevice));
   }
-  ctx->bas.Free(); ctx->frames.Free(); ctx->weno_scratch.Free();
+  ctx->bas.Free(); ctx->frames.Free(); ctx->weno_scratch.Free(); ctx->damping.Free(); ctx->energy_viscosity = false;
   if (ctx->cfg.diffusion != MCFD_INVISCID) {
     MCFD_CUDA(ctx, ctx->grad.Alloc((size_t)ctx->n_tiles * ctx->n_nodes * 15 * kTile));
     MCFD_CUDA(ctx, ctx->hn.Alloc((size_t)ctx->n_tiles * 6 * ctx->q * ctx->q * 15 * kTile));
@@ -572,6 +580,74 @@ int mcfd_set_diffusion(mcfd_ctx *ctx, double beta_0, double beta_1, double nu, d
   return MCFD_OK;
 }
 
+int mcfd_build_damping_matrices(mcfd_ctx *ctx) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (ctx->cfg.diffusion != MCFD_CELL_VISCOSITY_DDG)
+    return Fail(ctx, MCFD_ERR_STATE, "the context was not created with MCFD_CELL_VISCOSITY_DDG");
+  if (ctx->rk_order) return Fail(ctx, MCFD_ERR_STATE, "an RK step is open");
+  if (ctx->mesh.n_ghost) return Fail(ctx, MCFD_ERR_STATE, "the energy-based viscosity is built for parts without ghost cells");
+  const int n = ctx->n_nodes;
+  const size_t state = (size_t)ctx->n_tiles * ctx->fields * kTile;
+  MCFD_CUDA(ctx, ctx->damping.Alloc((size_t)ctx->n_tiles * n * n * kTile));
+  if (!ctx->visc_dt_bits.p) MCFD_CUDA(ctx, ctx->visc_dt_bits.Alloc(1));
+  if (ctx->res.n < state) MCFD_CUDA(ctx, ctx->res.Alloc(state));
+  // the probes use two of the three state buffers that do not hold the current solution
+  double *probe = ctx->u[(ctx->cur + 1) % 3].p;
+  const int threads = 256;
+  for (int col = 0; col < n; ++col) {   // viscosity.hpp:338-349: one unit nodal vector after the other
+    ProbeStateKernel<<<(int)((state + threads - 1) / threads), threads, 0, ctx->stream>>>(probe, ctx->fields,
+        (int)ctx->n_tiles, col);
+    if (int s = LaunchTrace(ctx, probe, 0, ctx->n_cells)) return s;
+    if (int s = LaunchStage(ctx, probe, probe, ctx->res.p, kModeProbe, 0.0, 0, ctx->total_blocks)) return s;
+    const int nl = (int)ctx->mesh.n_local;
+    if (ctx->q == 3) DampingColumnKernel<3><<<(nl + 127) / 128, 128, 0, ctx->stream>>>(ctx->res.p, ctx->geom.p, ctx->damping.p, col, nl);
+    else DampingColumnKernel<4><<<(nl + 127) / 128, 128, 0, ctx->stream>>>(ctx->res.p, ctx->geom.p, ctx->damping.p, col, nl);
+    ctx->launches += 2;
+  }
+  MCFD_CUDA(ctx, cudaGetLastError());
+  MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->energy_viscosity = true;
+  return MCFD_OK;
+}
+
+int mcfd_get_damping_matrices(mcfd_ctx *ctx, double *matrices) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (!ctx->damping.p || !matrices) return Fail(ctx, MCFD_ERR_STATE, "mcfd_build_damping_matrices has not been called");
+  const int n = ctx->n_nodes;
+  std::vector<double> tiles(ctx->damping.n);
+  MCFD_CUDA(ctx, cudaMemcpy(tiles.data(), ctx->damping.p, tiles.size() * sizeof(double), cudaMemcpyDeviceToHost));
+  for (int64_t c = 0; c < ctx->mesh.n_local; ++c)
+    for (int i = 0; i < n * n; ++i) matrices[c * n * n + i] = tiles[((size_t)(c >> 5) * n * n + i) * kTile + (c & 31)];
+  return MCFD_OK;
+}
+
+int mcfd_update_cell_viscosity(mcfd_ctx *ctx, double time_scale) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (!ctx->damping.p) return Fail(ctx, MCFD_ERR_STATE, "mcfd_build_damping_matrices has not been called");
+  MCFD_CUDA(ctx, EnsureTables(ctx));
+  double *u = HaloState(ctx);
+  TimeStepResetKernel<<<1, 1, 0, ctx->stream>>>(ctx->visc_dt_bits.p);
+  const int nl = (int)ctx->mesh.n_local, tiles = (nl + kTile - 1) / kTile;
+  if (ctx->q == 3) ViscosityKernel<3><<<tiles, 160, 0, ctx->stream>>>(u, ctx->geom.p, ctx->nbr.p, ctx->code.p, ctx->damping.p,
+      ctx->length.p, nl, time_scale, ctx->cell_nu.p, ctx->visc_dt_bits.p);
+  else ViscosityKernel<4><<<tiles, 160, 0, ctx->stream>>>(u, ctx->geom.p, ctx->nbr.p, ctx->code.p, ctx->damping.p,
+      ctx->length.p, nl, time_scale, ctx->cell_nu.p, ctx->visc_dt_bits.p);
+  MCFD_CUDA(ctx, cudaGetLastError());
+  ctx->launches += 2;
+  return MCFD_OK;
+}
+
+int mcfd_get_cell_viscosity(mcfd_ctx *ctx, double *nu) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (!ctx->cell_nu.p || !nu) return Fail(ctx, MCFD_ERR_STATE, "no per-cell viscosity in this context");
+  MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  std::vector<double> tiles(ctx->cell_nu.n);
+  MCFD_CUDA(ctx, cudaMemcpy(tiles.data(), ctx->cell_nu.p, tiles.size() * sizeof(double), cudaMemcpyDeviceToHost));
+  for (int64_t c = 0; c < ctx->n_cells; ++c)
+    for (int k = 0; k < 5; ++k) nu[c * 5 + k] = tiles[((size_t)(c >> 5) * 5 + k) * kTile + (c & 31)];
+  return MCFD_OK;
+}
+
 int mcfd_set_cell_viscosity(mcfd_ctx *ctx, int64_t n_cells, const double *nu) {
   if (int s = RequireMesh(ctx)) return s;
   if (ctx->cfg.diffusion != MCFD_CELL_VISCOSITY_DDG)
@@ -745,6 +821,13 @@ int mcfd_time_step_device(mcfd_ctx *ctx, double dt_guess, int rk_order, double *
   if (rk_order < 0 || rk_order > 4) return Fail(ctx, MCFD_ERR_ARG, "bad RK order");
   if (!ctx->dt_dev.p) MCFD_CUDA(ctx, ctx->dt_dev.Alloc(1));
   if (!dt_dev) dt_dev = ctx->dt_dev.p;
+  if (ctx->energy_viscosity) {   // WithViscosity::GetTimeStep (with_viscosity.hpp:67-71): CFL * min_dt_ of UpdateProperties
+    TimeStepFinishKernel<<<1, 1, 0, ctx->stream>>>(ctx->visc_dt_bits.p, kCfl[rk_order][ctx->cfg.degree], dt_guess,
+        ctx->cfg.scheme == MCFD_FR_LOBATTO, dt_dev);
+    MCFD_CUDA(ctx, cudaGetLastError());
+    ctx->launches += 1;
+    return MCFD_OK;
+  }
   TimeStepResetKernel<<<1, 1, 0, ctx->stream>>>(ctx->dt_bits.p);
   int n = (int)ctx->mesh.n_local, threads = 256, blocks = (n + kTile - 1) / kTile;
   if (ctx->q == 3) TimeStepKernel<3><<<blocks, threads, 0, ctx->stream>>>(ctx->u[ctx->cur].p, ctx->length.p, n, ctx->dt_bits.p);

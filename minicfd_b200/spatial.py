@@ -74,6 +74,19 @@ class Spatial:
         demo/laminar/cavity.cpp:30-38; ignored by inviscid systems (fr/general.hpp:455-459)."""
         self._set_bc(tag, capi.BC_NO_SLIP_WALL, func, time_dependent)
 
+    def EnableEnergyBasedViscosity(self, time_scale=1.0):
+        """Makes this object behave like `WithViscosity<General>` over `EnergyBasedViscosity<Part, Riemann>`
+        (spatial/with_viscosity.hpp:20-73, demo/euler/sourceless.hpp:82-103): damping matrices now
+        (Viscosity::Initialize), UpdateProperties after every SetSolutionColumn and Runge-Kutta stage, and the time
+        step from its min_dt_.  Single part only, like the reference's class statics."""
+        assert self.comm is None and self.part.n_ghost == 0
+        self.ctx.build_damping_matrices()
+        self._energy_time_scale = float(time_scale)
+
+    def UpdateProperties(self):
+        if getattr(self, "_energy_time_scale", None) is not None:
+            self.ctx.update_cell_viscosity(self._energy_time_scale)
+
     def SetCellViscosity(self, nu):
         """EnergyBasedViscosity::properties_ (viscosity.hpp:57, 564-566): nu[n_local + n_ghost][5]."""
         self.ctx.set_cell_viscosity(nu)
@@ -128,6 +141,7 @@ class Spatial:
             self.comm.drain()              # an exchange of the old state may still be in flight
         self.ctx.set_solution(column)
         self.Reconstruct()                 # with_limiter.hpp:57-61
+        self.UpdateProperties()            # with_viscosity.hpp:52-55
 
     def GetSolutionColumn(self):
         return self.ctx.get_solution()
@@ -174,7 +188,7 @@ class RungeKutta:
 
     def Update(self, system: Spatial, t, dt):
         ctx = system.ctx
-        if system._limiter is not None:
+        if system._limiter is not None or getattr(system, "_energy_time_scale", None) is not None:
             ctx.rk_begin(self.order, t, dt)
             self._stages_with_limiter(system)
             return
@@ -195,6 +209,7 @@ class RungeKutta:
             ctx.rk_stage_inner(stage)
             ctx.rk_stage_inter(stage)
             system.Reconstruct()
+            system.UpdateProperties()
 
     def _stages_with_halo(self, system: Spatial):
         """Every stage: the inner cells advance on the main stream (fem.hpp:249-254) while a high-priority
@@ -227,7 +242,7 @@ class RungeKutta:
     def UpdateDevice(self, system: Spatial, t, dt_ptr: int):
         """Update with the time step resident in device memory (no host round trip)."""
         ctx = system.ctx
-        if system._limiter is not None:
+        if system._limiter is not None or getattr(system, "_energy_time_scale", None) is not None:
             ctx.rk_begin_device(self.order, t, dt_ptr)
             self._stages_with_limiter(system)
             return

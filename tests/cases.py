@@ -148,3 +148,9 @@ def cell_viscosities(n_cells, seed=1):
     nu = rng.uniform(0.0, 0.05, (n_cells, 5))
     nu[rng.uniform(size=nu.shape) < 0.3] = 0.0
     return nu
+
+
+# ---- EnergyBasedViscosity + WithViscosity ----------------------------------------------------------
+ENERGY_GOLDEN_CASES = [("energy_p2_hllc", 2, 1), ("energy_p3_hllc", 3, 1)]
+ENERGY_BETAS = (2.0, 1.0 / 12)
+ENERGY_AMP = 5e-2          # noise level at which some, not all, (cell, component) pairs get a viscosity

@@ -100,6 +100,24 @@ def weno_lazy(mesh, degree, column_in, w0=0.001, eps=1e-6, *, n_local=None, n_gh
     return out
 
 
+def energy_viscosity(mesh, degree, betas, column=None, time_scale=1.0):
+    """(damping[n_cells][N][N], nu[n_cells][5] or None, min_dt or None) from the device code run on the host."""
+    cells = np.ascontiguousarray(mesh.cells, dtype=np.int64)
+    bfaces = np.ascontiguousarray(mesh.bfaces, dtype=np.int64)
+    btags = np.ascontiguousarray(mesh.btags, dtype=np.int32)
+    nodes = np.ascontiguousarray(mesh.nodes, dtype=np.float64)
+    n = (degree + 1) ** 3
+    damping = np.empty((len(cells), n, n)); nu = np.empty((len(cells), 5)); min_dt = C.c_double(0)
+    b = np.ascontiguousarray(betas, dtype=np.float64)
+    col = None if column is None else np.ascontiguousarray(column, dtype=np.float64)
+    rc = lib().emu_energy_viscosity(C.c_int(degree), C.c_int64(len(nodes)), _dp(nodes), C.c_int64(len(cells)), _ip(cells),
+                                    C.c_int64(len(bfaces)), _ip(bfaces), _i32(btags), _dp(b), _dp(col),
+                                    C.c_double(time_scale), _dp(damping), _dp(nu), C.byref(min_dt))
+    if rc != 0:
+        raise RuntimeError("emu_energy_viscosity failed")
+    return damping, (None if column is None else nu), (None if column is None else min_dt.value)
+
+
 def riemann(kind, n, ul, ur, bc=-1):
     out = np.empty(5)
     n = np.ascontiguousarray(n, dtype=np.float64)

@@ -57,6 +57,22 @@ def main():
         np.savez_compressed(os.path.join(HERE, name + ".npz"), u=u, residual=res, u_rk3=r.get_solution(),
                             nodes=m.nodes, cells=m.cells, bfaces=m.bfaces, btags=m.btags)
         print(name, np.linalg.norm(res))
+    # WithViscosity<fr::Lobatto<Part, EnergyBasedViscosity<Part, ConvectionDiffusion<Euler, Direct<Isotropic>>>>>
+    for name, degree, riemann in cases.ENERGY_GOLDEN_CASES:
+        r = refapi.Ref(m, degree=degree, scheme=refapi.FR_ENERGY_VISCOSITY, riemann=riemann,
+                       viscous=cases.ENERGY_BETAS + (0.0, 0.708))
+        cases.apply_bcs_ref(r)
+        u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), amp=cases.ENERGY_AMP)
+        damping = r.damping_matrices()          # zeroes the solution
+        r.set_solution(u)                       # SetSolutionColumn -> UpdateProperties
+        nu = r.cell_viscosity()
+        dt = r.time_step(1.0, 3)
+        res = r.residual(cases.GOLDEN_T)
+        r.rk_update(3, 0.0, cases.GOLDEN_DT, 1)
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), u=u, damping=damping[:4], nu=nu, dt=dt, residual=res,
+                            u_rk3=r.get_solution(), nu_rk3=r.cell_viscosity(),
+                            nodes=m.nodes, cells=m.cells, bfaces=m.bfaces, btags=m.btags)
+        print(name, int((nu > 0).sum()), "of", nu.size, "viscosities non-zero; dt", dt)
     # WithLimiter<fr::Lobatto, weno::Lazy>: the limiter's action on a column, and an RK3 step with it
     for name, degree, riemann in cases.WENO_GOLDEN_CASES:
         r = refapi.Ref(m, degree=degree, scheme=refapi.FR_WENO_LAZY, riemann=riemann, weno=cases.WENO)

@@ -220,6 +220,69 @@ int emu_weno_lazy(int degree, int64_t n_nodes, const double *xyz, int64_t n_loca
   return 0;
 }
 
+}  // extern "C"
+
+template <int Q, int CPB, int NW>
+static void RunEnergy(HostMesh const &mesh, const double *betas, const double *column, double time_scale,
+    double *damping_out, double *nu_out, double *min_dt_out) {
+  constexpr int N = Q * Q * Q, F = 5 * N;
+  using G = StageGeometry<Q, CPB, NW>;
+  const int64_t nl = mesh.n_local, nc = nl + mesh.n_ghost, nt = (nc + kTile - 1) / kTile;
+  auto geom = ToTiles(mesh.coef, kGeomRows, nc, nt);
+  auto nbr = ToTiles(mesh.nbr, 6, nc, nt);
+  auto code = ToTiles(mesh.code, 6, nc, nt);
+  auto h2s = ToTiles(mesh.h2s, 18, nc, nt);
+  std::vector<unsigned char> bkind(mesh.bound_faces.size() + 1, 0);
+  std::vector<double> bvals((mesh.bound_faces.size() + 1) * Q * Q * 5, 0.0);
+  std::vector<double> u((size_t)nt * F * kTile, 0.0), res(u.size(), 0.0), grad((size_t)nt * N * 15 * kTile, 0.0),
+      hn((size_t)nt * 6 * Q * Q * 15 * kTile, 0.0), damping((size_t)nt * N * N * kTile, 0.0), smem(G::kSharedBytes / 8 + 1);
+  StageArgs a;
+  a.u_in = u.data(); a.u0 = u.data(); a.u_out = res.data(); a.geom = geom.data(); a.nbr = nbr.data(); a.code = code.data();
+  a.bkind = bkind.data(); a.bvals = bvals.data(); a.n_local = (int)nl; a.block_begin = 0; a.mode = kModeResidual; a.dt = 0;
+  a.dt_dev = nullptr; a.grad = grad.data(); a.hn = hn.data(); a.h2s = h2s.data(); a.cell_nu = nullptr;
+  a.vis.beta0 = betas[0]; a.vis.beta1 = betas[1]; a.vis.nu = 0; a.vis.cond = 0;
+  const int n_blocks = (int)((nl + CPB - 1) / CPB);
+  for (int col = 0; col < N; ++col) {   // mcfd_build_damping_matrices
+    for (size_t i = 0; i < u.size(); ++i) u[i] = ((int)((i / kTile) % F) / 5 == col) ? 1.0 : 0.0;
+    RunTraceOnHost<Q>(u.data(), geom.data(), grad.data(), hn.data(), (int)nc);
+    for (int b = 0; b < n_blocks; ++b) RunStageBlockOnHost<Q, kHllc, CPB, NW, false, kDiffProbe>(a, b, smem.data());
+    for (int64_t c = 0; c < nl; ++c) for (int r = 0; r < N; ++r) {
+      double d[3], w;
+      QuadraturePoint<Q>(r, geom.data() + (c >> 5) * kGeomRows * kTile + (c & 31), kTile, d, &w);
+      damping[((c >> 5) * N * N + r * N + col) * kTile + (c & 31)] = res[((c >> 5) * F + r * 5) * kTile + (c & 31)] * w;
+    }
+  }
+  for (int64_t c = 0; c < nl; ++c) for (int i = 0; i < N * N; ++i) damping_out[c * N * N + i] = damping[((c >> 5) * N * N + i) * kTile + (c & 31)];
+  if (!column) return;
+  for (int64_t c = 0; c < nc; ++c) for (int f = 0; f < F; ++f) u[((c >> 5) * F + f) * kTile + (c & 31)] = column[c * F + f];
+  std::vector<double> length((size_t)nt * kTile, 1.0), nu((size_t)nt * 5 * kTile, 0.0);
+  for (int64_t c = 0; c < nl; ++c) length[c] = mesh.length[c];
+  std::vector<unsigned char> nn(6 * 8 * Q * Q);
+  for (int i = 0; i < 6 * 8 * Q * Q; ++i) nn[i] = c_tab.nbr_node[i / (8 * Q * Q)][(i / (Q * Q)) % 8][i % (Q * Q)];
+  double min_dt = 1e100;
+  for (int64_t c = 0; c < nl; ++c) for (int k = 0; k < 5; ++k)
+    min_dt = std::fmin(min_dt, ViscosityCell<Q>(u.data(), geom.data(), nbr.data(), code.data(), nn.data(), damping.data(),
+        length.data(), (int)(c >> 5), (int)(c & 31), k, time_scale, nu.data()));
+  for (int64_t c = 0; c < nl; ++c) for (int k = 0; k < 5; ++k) nu_out[c * 5 + k] = nu[((c >> 5) * 5 + k) * kTile + (c & 31)];
+  *min_dt_out = min_dt;
+}
+
+extern "C" {
+
+// EnergyBasedViscosity on the host: damping matrices [n_local][N][N] and, when a column is given, the viscosities
+// [n_local][5] and min_dt_ of UpdateProperties.
+int emu_energy_viscosity(int degree, int64_t n_nodes, const double *xyz, int64_t n_local, const int64_t *cell_nodes,
+    int64_t n_bfaces, const int64_t *bface_nodes, const int32_t *bface_tags, const double *betas, const double *column,
+    double time_scale, double *damping_out, double *nu_out, double *min_dt_out) {
+  const int q = degree + 1;
+  c_tab = BuildTables(degree, 0, (q == 3) ? kP2Warps : kP3Warps, kTile / ((q == 3) ? kP2Cells : kP3Cells));
+  HostMesh mesh;
+  if (!mesh.Build(degree, n_nodes, xyz, n_local, 0, cell_nodes, n_bfaces, bface_nodes, bface_tags, 0, nullptr)) return -1;
+  if (q == 3) RunEnergy<3, kP2Cells, kP2Warps>(mesh, betas, column, time_scale, damping_out, nu_out, min_dt_out);
+  else RunEnergy<4, kP3Cells, kP3Warps>(mesh, betas, column, time_scale, damping_out, nu_out, min_dt_out);
+  return 0;
+}
+
 // Boundary-face order and flux-point coordinates as the library defines them.
 int64_t emu_boundary(int degree, int64_t n_nodes, const double *xyz, int64_t n_local, int64_t n_ghost,
     const int64_t *cell_nodes, int64_t n_bfaces, const int64_t *bface_nodes, const int32_t *bface_tags,

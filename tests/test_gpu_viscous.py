@@ -186,3 +186,52 @@ def test_cell_viscosity_golden_and_table(name, degree, riemann):
         sp.SetSolutionColumn(g["u"])
         RungeKutta(order).Update(sp, 0.0, 1e-3)
         assert relerr(sp.GetSolutionColumn(), o.rk_update(g["u"], order, 0.0, 1e-3)) < TOL
+
+
+# ---- EnergyBasedViscosity + WithViscosity -------------------------------------------------------
+@pytest.mark.parametrize("name,degree,riemann", cases.ENERGY_GOLDEN_CASES)
+def test_energy_based_viscosity_golden(name, degree, riemann):
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    m = meshmod.HexMesh(nodes=g["nodes"], cells=g["cells"], bfaces=g["bfaces"], btags=g["btags"])
+    sp = Spatial(Part(m), degree=degree, riemann=riemann, device=0, diffusion=capi.CELL_VISCOSITY_DDG)
+    cases.apply_bcs_spatial(sp, cases.MIXED_BCS)
+    sp.SetDiffusion(*cases.ENERGY_BETAS, 0.0, 0.708)           # Direct::SetBetaValues before the spatial object exists
+    sp.EnableEnergyBasedViscosity()                            # WithViscosity(...): Viscosity::Initialize
+    assert relerr(sp.ctx.damping_matrices()[:4], g["damping"]) < TOL
+    sp.SetSolutionColumn(g["u"])                               # -> UpdateProperties
+    nu = sp.ctx.cell_viscosity()
+    assert np.array_equal(nu > 0, g["nu"] > 0)
+    assert relerr(nu, g["nu"]) < TOL
+    assert sp.GetTimeStep(1.0, 3) == pytest.approx(float(g["dt"]), rel=1e-13)
+    sp.SetTime(cases.GOLDEN_T)
+    assert relerr(sp.GetResidualColumn(), g["residual"]) < TOL
+    RungeKutta(3).Update(sp, 0.0, cases.GOLDEN_DT)
+    assert relerr(sp.GetSolutionColumn(), g["u_rk3"]) < 1e-11
+    assert relerr(sp.ctx.cell_viscosity(), g["nu_rk3"]) < 1e-9
+
+
+def test_energy_based_viscosity_properties_at_size():
+    """Smooth data gets no viscosity at all; a jump switches it on only next to the jump; it never exceeds
+    lambda_max h / P; the damping matrices are negative semi-definite in the quadrature-weighted sense
+    (u^T D u <= 0, the assert of viscosity.hpp:520)."""
+    m = meshmod.box(12, 10, 8, hi=(1.2, 1.0, 0.8))
+    sp = Spatial(Part(m), degree=2, riemann=capi.HLLC, device=0, diffusion=capi.CELL_VISCOSITY_DDG)
+    for tag in range(6):
+        sp.SetInviscidWall(tag)
+    sp.SetDiffusion(*cases.ENERGY_BETAS, 0.0, 0.708)
+    sp.EnableEnergyBasedViscosity()
+    pts = cell_points(m.nodes, m.cells, 2)
+    smooth = fields.smooth(0.5)(pts, 0.0)
+    sp.SetSolutionColumn(smooth.reshape(-1))
+    assert sp.ctx.cell_viscosity().max() == 0.0
+    xc = pts[..., 0].mean(1)
+    jumped = smooth.copy()
+    jumped[xc > 0.6] *= 1.5                                     # whole cells: x = 0.6 is a plane of faces
+    sp.SetSolutionColumn(jumped.reshape(-1))
+    nu = sp.ctx.cell_viscosity()
+    near = np.abs(xc - 0.6) < 0.11
+    assert nu[near].max() > 0 and nu[~near].max() == 0.0
+    D = sp.ctx.damping_matrices()
+    rng = np.random.default_rng(0)
+    v = rng.normal(size=(len(D), 27))
+    assert (np.einsum("ci,cij,cj->c", v, D, v) <= 1e-12).all()

@@ -156,6 +156,19 @@ def test_cell_viscosity_kernel_source_on_host(name, degree, riemann):
     assert relerr(emuapi.stage(m, degree, 0, riemann, g["u"], cell_nu=nu, **kw), o.residual(g["u"], cases.GOLDEN_T)) < 1e-12
 
 
+@pytest.mark.parametrize("name,degree,riemann", cases.ENERGY_GOLDEN_CASES)
+def test_energy_viscosity_kernel_source_on_host_matches_golden(name, degree, riemann):
+    """Probe launches of the trace + stage kernels -> damping matrices; ViscosityCell -> viscosities and min_dt_."""
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    m = meshmod.HexMesh(nodes=g["nodes"], cells=g["cells"], bfaces=g["bfaces"], btags=g["btags"])
+    damping, nu, min_dt = emuapi.energy_viscosity(m, degree, cases.ENERGY_BETAS, g["u"])
+    assert relerr(damping[:4], g["damping"]) < 1e-12
+    assert np.array_equal(nu > 0, g["nu"] > 0)
+    assert relerr(nu, g["nu"]) < 1e-12
+    cfl = {2: 0.209, 3: 0.130}[degree] * 2
+    assert min(1.0, cfl * min_dt) == pytest.approx(float(g["dt"]), rel=1e-13)
+
+
 @pytest.mark.parametrize("name,degree,riemann", cases.WENO_EIGEN_GOLDEN_CASES)
 def test_weno_eigen_kernel_source_on_host_matches_golden(name, degree, riemann):
     g = np.load(os.path.join(GOLDEN, name + ".npz"))

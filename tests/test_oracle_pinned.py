@@ -162,6 +162,38 @@ def test_c_oracle_isotropic_diffusion_matches_golden(name, degree, riemann):
     assert relerr(o.residual(g["u"], cases.GOLDEN_T), g["residual"]) < TOL
 
 
+@pytest.mark.parametrize("name,degree,riemann", cases.ENERGY_GOLDEN_CASES)
+def test_c_oracle_energy_based_viscosity_matches_golden(name, degree, riemann):
+    """EnergyBasedViscosity: damping matrices, UpdateProperties, the residual with the resulting
+    per-cell viscosities, and an RK3 step that updates them after every stage."""
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    o = oc.Oracle(_golden_mesh(g), degree, 6, riemann)
+    cases.apply_bcs_oracle(o)
+    o.set_viscous(*cases.ENERGY_BETAS, 0.0, 0.708)
+    damping = o.damping_matrices()
+    assert relerr(damping[:4], g["damping"]) < TOL
+    nu, min_dt = o.update_viscosity(g["u"], damping)
+    assert np.array_equal(nu > 0, g["nu"] > 0) and 0 < (nu > 0).sum() < nu.size
+    assert relerr(nu, g["nu"]) < TOL
+    cfl = {2: 0.209, 3: 0.130}[degree] * 2
+    assert min(1.0, cfl * min_dt) == pytest.approx(float(g["dt"]), rel=1e-13)
+    o.set_cell_viscosity(nu)
+    assert relerr(o.residual(g["u"], cases.GOLDEN_T), g["residual"]) < TOL
+    # RungeKutta<3>::Update on a WithViscosity system: UpdateProperties after every SetSolutionColumn
+    u, dt = g["u"].copy(), cases.GOLDEN_DT
+    def euler(uu, tt):
+        return uu + dt * o.residual(uu, tt)
+    def set_solution(uu):
+        o.set_cell_viscosity(o.update_viscosity(uu, damping)[0])
+        return uu
+    u0 = u
+    u1 = set_solution(euler(u0, 0.0))
+    u2 = set_solution((u0 * 3 + euler(u1, dt)) / 4)
+    u3 = set_solution((euler(u2, dt / 2) * 2 + u0) / 3)
+    assert relerr(u3, g["u_rk3"]) < 1e-11
+    assert relerr(o.update_viscosity(u3, damping)[0], g["nu_rk3"]) < 1e-9
+
+
 def _flux_1d(rho, u, p):
     """Flux of a 1-D primitive state (test/riemann/euler/exact.cpp:34-39)."""
     e = p / 0.4 + 0.5 * rho * u * u
