@@ -52,6 +52,9 @@ def parse():
                     help="run the Navier-Stokes + direct-DG path with this kinematic viscosity (not the headline workload)")
     ap.add_argument("--limiter", action="store_true",
                     help="WithLimiter<.., weno::Lazy(0.001, 1e-6)>: the WENO limiter after every stage (not the headline workload)")
+    ap.add_argument("--energy-viscosity", action="store_true",
+                    help="WithViscosity<.., EnergyBasedViscosity>: artificial viscosity updated after every stage "
+                         "(not the headline workload; single GPU)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of replaying a CUDA graph")
@@ -138,18 +141,25 @@ def cpu_run(args, steps, warmup, cells=None):
         scheme = 3
     if args.limiter:
         scheme = 4
+    if args.energy_viscosity:
+        scheme = 7
     riemann = RIEMANN[args.riemann]
     kf = 5 * (args.degree + 1) ** 3
     if refapi.available(args.degree):
         kind = "reference"
         n_parts = max(1, min(cores, 64))
+        if args.energy_viscosity:
+            n_parts = 1        # EnergyBasedViscosity keeps its state in class statics: one spatial object per process
         # ~8e6 DOF-updates/s/core; aim at ~1.5 s per step
         n = cells or args.cpu_cells or int(round((n_parts * 8e6 * 1.5 / (3 * kf)) ** (1 / 3)))
         n = max(6, min(n, 48))
+        if args.energy_viscosity:
+            n = cells or args.cpu_cells or 12      # BuildDampingMatrices costs ~5 ms per cell
         m = meshmod.box(n, n, n, hi=(10.0, 10.0, 10.0))
         px, py, pz = meshmod.factor3(n_parts)
         parts = meshmod.block_partition(m, px, py, pz)
-        r = refapi.Ref(m, degree=args.degree, scheme=scheme, riemann=riemann, cell_parts=parts, n_parts=n_parts)
+        r = refapi.Ref(m, degree=args.degree, scheme=scheme, riemann=riemann, cell_parts=parts, n_parts=n_parts,
+                       viscous=(2.0, 1.0 / 12, 0.0, 0.708) if args.energy_viscosity else None)
         if args.viscous is not None:
             r.set_viscous(2.0, 1.0 / 12, args.viscous, 0.708)
         for tag in range(6):
@@ -195,6 +205,7 @@ def config_dict(args, n_gpus, dims, part):
                         + ("Euler isentropic vortex, " if args.viscous is None else
                            f"Navier-Stokes (nu={args.viscous}, direct-DG face flux) on the isentropic vortex, ") +
                         ("weno::Lazy limiter after every stage, " if args.limiter else "") +
+                        ("EnergyBasedViscosity updated after every stage, " if args.energy_viscosity else "") +
                         
                         f"{args.scheme.upper()}-Lobatto p={args.degree}, {args.riemann.upper()}, RK3, periodic",
             "cells_per_gpu": args.cells ** 3, "dof_per_gpu": args.cells ** 3 * 5 * (args.degree + 1) ** 3,
@@ -253,7 +264,11 @@ def ours(args):
     scheme = capi.FR_LOBATTO if args.scheme == "fr" else capi.DG_LOBATTO
     comm = halo.for_part(part, 5 * (args.degree + 1) ** 3) if world > 1 else None
     sp = Spatial(part, scheme=scheme, degree=args.degree, riemann=RIEMANN[args.riemann], device=local_rank,
-                 comm=comm, diffusion=capi.INVISCID if args.viscous is None else capi.NAVIER_STOKES_DDG)
+                 comm=comm, diffusion=capi.CELL_VISCOSITY_DDG if args.energy_viscosity else
+                 (capi.INVISCID if args.viscous is None else capi.NAVIER_STOKES_DDG))
+    if args.energy_viscosity:
+        sp.SetDiffusion(2.0, 1.0 / 12, 0.0, 0.708)
+        sp.EnableEnergyBasedViscosity()
     if args.viscous is not None:
         sp.SetDiffusion(2.0, 1.0 / 12, args.viscous, 0.708)
     if args.limiter:
