@@ -667,7 +667,7 @@ MCFD_HD void StagePhaseB2(const StageArgs &p, int tid, int bid, double *smem) {
         const int b = -1 - cur.nb;
         const int kind = p.bkind[b];
         const double inv = sgn * inv_area;
-        if (kViscous && kind == kBcNoSlip) {
+        if (kViscous && !kGeneral && kind == kBcNoSlip) {   // fr::General leaves AddFluxOnNoSlipWalls empty (fem.hpp:382-383)
           // fr/lobatto.hpp:301-319, fr/general.hpp:460-479: inviscid-wall flux minus the viscous flux
           // with the velocity penalty beta0/dist; `given` = (-, wall velocity, n . grad T)
           const double *gv = p.bvals + ((size_t)b * FQ + q) * 5;
@@ -703,6 +703,28 @@ MCFD_HD void StagePhaseB2(const StageArgs &p, int tid, int bid, double *smem) {
             fm[1][x] = cur.u[1] * vel[x]; fm[2][x] = cur.u[2] * vel[x]; fm[3][x] = cur.u[3] * vel[x];
             fm[1 + x][x] += pr.p;
             fm[4][x] = h0 * vel[x];
+          }
+          if (kViscous == kDiffNavierStokes || kViscous == kDiffIsotropic) {   // the cached flux carried the viscous part too
+            const double *go = p.grad + ((size_t)g.tile * G::N * 15 + n * 15) * kTile + g.tl;
+            double gr[3][5], fx[3][5];
+#pragma unroll
+            for (int x = 0; x < 3; ++x) {
+#pragma unroll
+              for (int c = 0; c < 5; ++c) { gr[x][c] = go[(x * 5 + c) * kTile]; fx[x][c] = fm[c][x]; }
+            }
+            if (kViscous == kDiffNavierStokes) {
+              NsMinusFluxMatrix(p.vis, cur.u, gr, fx);
+            } else {
+              double nu[5];
+#pragma unroll
+              for (int c = 0; c < 5; ++c) nu[c] = p.cell_nu[((size_t)g.tile * 5 + c) * kTile + g.tl];
+              IsoMinusFluxMatrix(nu, gr, fx);
+            }
+#pragma unroll
+            for (int x = 0; x < 3; ++x) {
+#pragma unroll
+              for (int c = 0; c < 5; ++c) fm[c][x] = fx[x][c];
+            }
           }
 #pragma unroll
           for (int c = 0; c < 5; ++c) fl[c] = fm[c][0] * nx + fm[c][1] * ny + fm[c][2] * nz;

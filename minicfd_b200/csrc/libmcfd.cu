@@ -150,12 +150,12 @@ cudaError_t LaunchStageQ(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
   }
 }
 
-template <int Q, int CPB, int NW, int kDiff>
+template <int Q, int CPB, int NW, int kDiff, bool kGeneral = false>
 cudaError_t LaunchStageDiffusive(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
   switch (ctx->cfg.riemann) {
-  case MCFD_EXACT: return LaunchStageG<Q, kExact, CPB, NW, false, kDiff>(ctx, a, n_blocks);
-  case MCFD_HLLC: return LaunchStageG<Q, kHllc, CPB, NW, false, kDiff>(ctx, a, n_blocks);
-  default: return LaunchStageG<Q, kAusm, CPB, NW, false, kDiff>(ctx, a, n_blocks);
+  case MCFD_EXACT: return LaunchStageG<Q, kExact, CPB, NW, kGeneral, kDiff>(ctx, a, n_blocks);
+  case MCFD_HLLC: return LaunchStageG<Q, kHllc, CPB, NW, kGeneral, kDiff>(ctx, a, n_blocks);
+  default: return LaunchStageG<Q, kAusm, CPB, NW, kGeneral, kDiff>(ctx, a, n_blocks);
   }
 }
 template <int Q, int CPB, int NW>
@@ -165,6 +165,8 @@ cudaError_t LaunchStageViscous(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) 
     b.mode = kModeResidual;
     return LaunchStageG<Q, kHllc, CPB, NW, false, kDiffProbe>(ctx, b, n_blocks);
   }
+  if (ctx->cfg.scheme == MCFD_FR_GENERAL)   // fr::General on the Navier-Stokes Riemann type
+    return LaunchStageDiffusive<Q, CPB, NW, kDiffNavierStokes, true>(ctx, a, n_blocks);
   return ctx->cfg.diffusion == MCFD_NAVIER_STOKES_DDG ? LaunchStageDiffusive<Q, CPB, NW, kDiffNavierStokes>(ctx, a, n_blocks)
                                                       : LaunchStageDiffusive<Q, CPB, NW, kDiffIsotropic>(ctx, a, n_blocks);
 }
@@ -316,8 +318,12 @@ int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
     return Fail(nullptr, MCFD_ERR_ARG, "unknown Riemann solver");
   if (config->diffusion < MCFD_INVISCID || config->diffusion > MCFD_CELL_VISCOSITY_DDG)
     return Fail(nullptr, MCFD_ERR_ARG, "unknown diffusion model");
-  if (config->diffusion != MCFD_INVISCID && config->scheme != MCFD_FR_LOBATTO)
-    return Fail(nullptr, MCFD_ERR_ARG, "the viscous path is built for MCFD_FR_LOBATTO only");
+  // the reference's DG schemes carry no diffusive terms at all (spatial/dg/*.hpp); fr::General has them for any Riemann
+  // type, built here for Navier-Stokes
+  if (config->diffusion != MCFD_INVISCID && config->scheme == MCFD_DG_LOBATTO)
+    return Fail(nullptr, MCFD_ERR_ARG, "the reference's DG schemes have no diffusive terms; use MCFD_FR_LOBATTO or MCFD_FR_GENERAL");
+  if (config->diffusion == MCFD_CELL_VISCOSITY_DDG && config->scheme != MCFD_FR_LOBATTO)
+    return Fail(nullptr, MCFD_ERR_ARG, "MCFD_CELL_VISCOSITY_DDG is built for MCFD_FR_LOBATTO only");
   int n_dev = 0;
   cudaError_t e = cudaGetDeviceCount(&n_dev);
   if (e != cudaSuccess || n_dev == 0)

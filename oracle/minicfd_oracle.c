@@ -463,6 +463,11 @@ static void match_side(const oracle_t *o, int64_t cell, int lf, const double *fx
   }
 }
 
+/* scheme 8 = fr::General (Vincent correction over the whole node line) on the Navier-Stokes Riemann type */
+#define IS_NS(o) ((o)->scheme == 3 || (o)->scheme == 8)
+#define IS_GENERAL(o) ((o)->scheme == 2 || (o)->scheme == 8)
+#define IS_LUMPED_FR(o) ((o)->scheme == 0 || (o)->scheme == 3 || (o)->scheme == 6)
+
 void *oracle_create(int degree, int scheme, int riemann, int64_t n_nodes, const double *nodes,
     int64_t n_cells, const int64_t *cn, int64_t n_bfaces, const int64_t *bf, const int32_t *btag) {
   (void)n_nodes;
@@ -821,10 +826,10 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
     for (int a = 0; a < n; ++a) {
       double F[5][3];
       flux_matrix(&u[(c * n + a) * K], F);
-      if (o->scheme == 3 || o->scheme == 6) { /* fem.hpp:397-404 */
+      if (IS_NS(o) || o->scheme == 6) { /* fem.hpp:397-404 */
         double gc[3][5];
         global_gradient(o, u, c, a, gc);
-        if (o->scheme == 3) {
+        if (IS_NS(o)) {
           ns_minus_flux_matrix(o, F, &u[(c * n + a) * K], gc);
         } else {
           double nu[5];
@@ -875,14 +880,14 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
       if (cs >= 0) {
         int as = o->s_node[f * fq + p];
         flux_upwind(o->riemann, fr, uh, &u[(cs * n + as) * K], fu);
-        if (o->scheme == 3 || o->scheme == 6) { /* fr/general.hpp:316-350 */
+        if (IS_NS(o) || o->scheme == 6) { /* fr/general.hpp:316-350 */
           const double *us = &u[(cs * n + as) * K];
           double gh_[3][5], gs_[3][5], hh[6][5], hs[6][5], gcm[3][5], ucm[5];
           global_gradient_hessian(o, u, ch, ah, gh_, hh);
           global_gradient_hessian(o, u, cs, as, gs_, hs);
           ddg_common_gradient(o, o->dist[f * fq + p], fr->a, uh, us, gh_, gs_, hh, hs, gcm);
           for (int k = 0; k < 5; ++k) ucm[k] = (uh[k] + us[k]) / 2;
-          if (o->scheme == 3) {
+          if (IS_NS(o)) {
             ns_minus_flux_normal(o, fu, ucm, gcm, fr->a);
           } else { /* property = (holder's + sharer's) / 2, fr/general.hpp:331-335 */
             double nh[5], nsh[5];
@@ -891,7 +896,7 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
             iso_minus_flux_normal(fu, nh, gcm, fr->a);
           }
         }
-        if (o->scheme == 2) { /* fr/general.hpp:296-315, 409-434: the whole node line is corrected */
+        if (IS_GENERAL(o)) { /* fr/general.hpp:296-315, 409-434: the whole node line is corrected */
           double sh = o->h_scale[f * fq + p], ss = o->s_scale[f * fq + p];
           const double *Fh = &fhat[(ch * n + ah) * 15], *Fs = &fhat[(cs * n + as) * 15];
           int strd[3] = {fq, q, 1};
@@ -909,7 +914,7 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
               }
             }
           }
-        } else if (o->scheme == 0 || o->scheme == 3 || o->scheme == 6) { /* fr/general.hpp:296-315, fr/lobatto.hpp:232-251 */
+        } else if (IS_LUMPED_FR(o)) { /* fr/general.hpp:296-315, fr/lobatto.hpp:232-251 */
           double sh = o->h_scale[f * fq + p], ss = o->s_scale[f * fq + p];
           double gh = sh > 0 ? gp : -gp, gs = ss > 0 ? gp : -gp;
           const double *Fh = &fhat[(ch * n + ah) * 15], *Fs = &fhat[(cs * n + as) * 15];
@@ -932,11 +937,12 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
         if (kind >= 2) eval_field(o->field_kind[tag], o->field_prm[tag], &o->fxyz[(f * fq + p) * 3], t, given);
         if (kind == 6) { /* no-slip wall: fr/lobatto.hpp:301-319, fr/general.hpp:460-479; no term at all for
                             inviscid systems (fr/general.hpp:455-459) */
-          if (o->scheme != 3 && o->scheme != 6) continue;
+          /* fr::General does not override AddFluxOnNoSlipWalls (fem.hpp:382-383): nothing at all there either */
+          if ((!IS_NS(o) && o->scheme != 6) || IS_GENERAL(o)) continue;
           double gh_[3][5];
           boundary_flux(o->riemann, 0, fr, uh, given, fu);
           global_gradient(o, u, ch, ah, gh_);
-          if (o->scheme == 3) {
+          if (IS_NS(o)) {
             ns_minus_flux_no_slip(o, fu, given, uh, gh_, fr->a, o->beta0 / o->dist[f * fq + p]);
           } else { /* linear.hpp:85-91: the plain normal flux of the cell's own gradient */
             double nu[5];
@@ -946,7 +952,7 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
         } else {
           boundary_flux(o->riemann, kind, fr, uh, given, fu);
         }
-        if (o->scheme == 2) { /* fr/general.hpp:435-640 */
+        if (IS_GENERAL(o)) { /* fr/general.hpp:435-640 */
           double sh = o->h_scale[f * fq + p];
           const double *Fh = &fhat[(ch * n + ah) * 15];
           int strd[3] = {fq, q, 1}, d = o->h_dir[f];
@@ -957,7 +963,7 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
             for (int k = 0; k < 5; ++k)
               res[(ch * n + base + i * strd[d]) * K + k] -= (fu[k] * sh - Fh[k * 3 + d]) * gpr;
           }
-        } else if (o->scheme == 0 || o->scheme == 3 || o->scheme == 6) { /* fr/lobatto.hpp:278-428 */
+        } else if (IS_LUMPED_FR(o)) { /* fr/lobatto.hpp:278-428 */
           double sh = o->h_scale[f * fq + p], gh = sh > 0 ? gp : -gp;
           const double *Fh = &fhat[(ch * n + ah) * 15];
           for (int k = 0; k < 5; ++k) res[(ch * n + ah) * K + k] -= (fu[k] * sh - Fh[k * 3 + o->h_dir[f]]) * gh;
@@ -1037,7 +1043,7 @@ double oracle_time_step(void *h, const double *u, double dt_guess, int rk_order)
   }
   double dt = cfl[rk_order][o->degree] * min_dt;
   if (dt_guess < dt) dt = dt_guess;
-  if (o->scheme == 0 || o->scheme == 3 || o->scheme == 6) { dt *= 2.0; if (dt_guess < dt) dt = dt_guess; }
+  if (IS_LUMPED_FR(o)) { dt *= 2.0; if (dt_guess < dt) dt = dt_guess; }
   return dt;
 }
 

@@ -835,6 +835,11 @@ static SolverBase *Create(int scheme, int riemann, GlobalMesh &&mesh) {
     case 0: return new SolverImpl<sp::WithLimiter<sp::fr::Lobatto<ModalPart, RExact>, mini::limiter::weno::Eigen<Cell, RExact>>>(std::move(mesh));
     case 1: return new SolverImpl<sp::WithLimiter<sp::fr::Lobatto<ModalPart, RHllc>, mini::limiter::weno::Eigen<Cell, RHllc>>>(std::move(mesh));
     }
+  } else if (scheme == 8) {   // fr::General with an arbitrary Vincent c on the Navier-Stokes Riemann type
+    switch (riemann) {
+    case 0: return new SolverImpl<sp::fr::General<Part, VExact>>(std::move(mesh), g_c_next);
+    case 1: return new SolverImpl<sp::fr::General<Part, VHllc>>(std::move(mesh), g_c_next);
+    }
   } else if (scheme == 7) {   // single part only: EnergyBasedViscosity keeps its state in class statics
     if (mesh.n_parts != 1) return nullptr;
     switch (riemann) {

@@ -235,3 +235,22 @@ def test_energy_based_viscosity_properties_at_size():
     rng = np.random.default_rng(0)
     v = rng.normal(size=(len(D), 27))
     assert (np.einsum("ci,cij,cj->c", v, D, v) <= 1e-12).all()
+
+
+@pytest.mark.parametrize("degree,c_next,riemann", [(2, 0.3, capi.HLLC), (3, 0.8, capi.EXACT)])
+def test_fr_general_with_navier_stokes(degree, c_next, riemann):
+    """fr::General (Vincent correction over the whole node line) on the Navier-Stokes Riemann type; no-slip walls
+    contribute nothing there (fr::General does not override AddFluxOnNoSlipWalls, fem.hpp:382-383)."""
+    m = cases.small_mesh(seed=6)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), seed=8, amp=1e-4)
+    o = oc.Oracle(m, degree, 8, riemann, c_next=c_next)
+    cases.apply_viscous_oracle(o)
+    sp = Spatial(Part(m), scheme=capi.FR_GENERAL, degree=degree, riemann=riemann, device=0, fr_c_next=c_next,
+                 diffusion=capi.NAVIER_STOKES_DDG)
+    cases.apply_viscous_spatial(sp)
+    sp.SetSolutionColumn(u)
+    sp.SetTime(0.2)
+    assert relerr(sp.GetResidualColumn(), o.residual(u, 0.2)) < TOL
+    assert sp.GetTimeStep(1.0, 3) == pytest.approx(o.time_step(u, 1.0, 3), rel=1e-13)
+    RungeKutta(3).Update(sp, 0.0, 1e-3)
+    assert relerr(sp.GetSolutionColumn(), o.rk_update(u, 3, 0.0, 1e-3)) < TOL

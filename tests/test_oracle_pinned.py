@@ -194,6 +194,22 @@ def test_c_oracle_energy_based_viscosity_matches_golden(name, degree, riemann):
     assert relerr(o.update_viscosity(u3, damping)[0], g["nu_rk3"]) < 1e-9
 
 
+@pytest.mark.skipif(not refapi.available(2), reason="oracle/_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("degree,riemann,c_next", [(2, 1, 0.3), (3, 0, 0.8)])
+def test_c_oracle_fr_general_navier_stokes_matches_reference(degree, riemann, c_next):
+    m = cases.small_mesh()
+    r = refapi.Ref(m, degree=degree, scheme=refapi.FR_GENERAL_VISCOUS, riemann=riemann, c_next=c_next)
+    cases.apply_viscous_ref(r)
+    o = oc.Oracle(m, degree, 8, riemann, c_next=c_next)
+    cases.apply_viscous_oracle(o)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), amp=1e-4)
+    r.set_solution(u)
+    assert relerr(o.residual(u, 0.2), r.residual(0.2)) < TOL
+    assert o.time_step(u, 1.0, 3) == r.time_step(1.0, 3)
+    r.rk_update(3, 0.0, 1e-3, 1)
+    assert relerr(o.rk_update(u, 3, 0.0, 1e-3), r.get_solution()) < TOL
+
+
 def _flux_1d(rho, u, p):
     """Flux of a 1-D primitive state (test/riemann/euler/exact.cpp:34-39)."""
     e = p / 0.4 + 0.5 * rho * u * u
