@@ -71,6 +71,8 @@ struct Lobatto {  // integrator/lobatto.hpp:20-93
 namespace polynomial {
 template <class Gx, class Gy, class Gz, int kComponents, bool kL = false>
 struct Hexahedron {  // polynomial/hexahedron.hpp:41-65
+  static_assert(!kL, "libminicfd_b200 implements the kLocal == false expansion only (coefficients = nodal values of u); "
+                     "Hexahedron<..., true> stores det(J) u and changes gradients, Hessians and the residual scaling");
   static_assert(Gx::Q == Gy::Q && Gy::Q == Gz::Q, "the B200 path needs the same rule in all directions");
   static_assert(Gx::Q == 3 || Gx::Q == 4, "degree 2 or 3");
   static_assert(!kL, "kLocal = true (laminar demos) is not built yet");
