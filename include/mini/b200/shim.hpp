@@ -75,7 +75,6 @@ struct Hexahedron {  // polynomial/hexahedron.hpp:41-65
                      "Hexahedron<..., true> stores det(J) u and changes gradients, Hessians and the residual scaling");
   static_assert(Gx::Q == Gy::Q && Gy::Q == Gz::Q, "the B200 path needs the same rule in all directions");
   static_assert(Gx::Q == 3 || Gx::Q == 4, "degree 2 or 3");
-  static_assert(!kL, "kLocal = true (laminar demos) is not built yet");
   using Scalar = typename Gx::Scalar;
   using IntegratorX = Gx;
   static constexpr bool kLocal = kL;
