@@ -388,13 +388,16 @@ static double vincent_right_derivative(int degree, double c_next, double x) { /*
   return 0.5 * (curr + cp * prev + c_next * next);
 }
 
-typedef struct {
+typedef struct oracle_s {
   int degree, q, n, scheme, riemann;   /* scheme: 0 fr::Lobatto, 1 dg::Lobatto, 2 fr::General,
                                           3 fr::Lobatto on ConvectionDiffusion<Euler, Direct<NavierStokes>> */
   double beta0, beta1, nu, prandtl;    /* direct.hpp:31-32, navier_stokes.hpp:54 (class statics there) */
   double d2[MAXQ][MAXQ];               /* d2[i][m] = l_m''(x_i) */
   double *jtgrad;   /* [cell][n][3][3][3] d(J^-T)/d(xi_a) = mat_after_grad_of_U_, hexahedron.hpp:233-236 */
   double *dist;     /* [face][q*q] normal . HolderToSharer, fem.hpp:83-85 */
+  /* scheme 9 = dg::General on the modal Projection polynomial with Gauss-Legendre rules */
+  int kf;           /* doubles per cell in a column: 5 n (nodal) or 5 M (modal) */
+  void *dgm;        /* dgm_t, see the end of this file */
   double *cell_nu;  /* scheme 6: [cell][5] viscosity of every component, constant inside a cell: what
                        EnergyBasedViscosity::GetPropertyOnCell returns (viscosity.hpp:68-71); null = uniform nu */
   int limited;      /* WithLimiter<.., weno::Lazy>(w0, eps): the limiter follows every SetSolutionColumn */
@@ -467,6 +470,12 @@ static void match_side(const oracle_t *o, int64_t cell, int lf, const double *fx
 #define IS_NS(o) ((o)->scheme == 3 || (o)->scheme == 8)
 #define IS_GENERAL(o) ((o)->scheme == 2 || (o)->scheme == 8)
 #define IS_LUMPED_FR(o) ((o)->scheme == 0 || (o)->scheme == 3 || (o)->scheme == 6)
+
+static void dgm_setup(struct oracle_s *o, const double *nodes, const int64_t *cn);
+static void dgm_free(struct oracle_s *o);
+static void dgm_residual(struct oracle_s *o, double t, const double *u, double *res);
+static double dgm_min_dt(struct oracle_s *o, const double *u);
+static void dgm_approximate(struct oracle_s *o, int field_kind, const double *prm, double *column);
 
 void *oracle_create(int degree, int scheme, int riemann, int64_t n_nodes, const double *nodes,
     int64_t n_cells, const int64_t *cn, int64_t n_bfaces, const int64_t *bf, const int32_t *btag) {
@@ -617,11 +626,14 @@ void *oracle_create(int degree, int scheme, int riemann, int64_t n_nodes, const 
       match_side(o, o->sharer[f], sface[f], &o->fxyz[f * fq * 3], &o->s_node[f * fq], &o->s_dir[f], &o->s_scale[f * fq]);
   }
   free(hface); free(sface);
+  o->kf = 5 * n;
+  if (scheme == 9) dgm_setup(o, nodes, cn);
   return o;
 }
 
 void oracle_destroy(void *h) {
   oracle_t *o = h;
+  dgm_free(o);
   free(o->cell_nu); free(o->jtgrad); free(o->dist); free(o->xyz); free(o->jstar); free(o->jinv); free(o->det); free(o->length); free(o->holder); free(o->sharer);
   free(o->tag); free(o->h_node); free(o->s_node); free(o->h_dir); free(o->s_dir); free(o->h_scale);
   free(o->s_scale); free(o->frame); free(o->fweight); free(o->fxyz); free(o);
@@ -652,6 +664,7 @@ void oracle_approximate(void *h, int field_kind, const double *prm, double *colu
   oracle_t *o = h;
   double p8[8] = {0};
   for (int k = 0; k < 8 && prm; ++k) p8[k] = prm[k];
+  if (o->scheme == 9) { dgm_approximate(o, field_kind, p8, column); return; }
   for (int64_t i = 0; i < o->n_cells * o->n; ++i) eval_field(field_kind, p8, &o->xyz[i * 3], 0.0, &column[i * 5]);
 }
 
@@ -818,6 +831,7 @@ static void ddg_common_gradient(const oracle_t *o, double dist, const double *nr
 
 void oracle_residual(void *h, double t, const double *u, double *res) {
   oracle_t *o = h;
+  if (o->scheme == 9) { dgm_residual(o, t, u, res); return; }
   int q = o->q, n = o->n, fq = q * q, K = 5;
   int64_t nc = o->n_cells;
   double *fhat = malloc(sizeof(double) * nc * n * 15); /* flux_matrices_ cache, fr/general.hpp:213-215 */
@@ -994,7 +1008,7 @@ void oracle_set_limiter(void *h, int on, double w0, double eps) {
    under WithLimiter is followed by the limiter (spatial/with_limiter.hpp:57-61) */
 void oracle_rk_update(void *h, int order, double t, double dt, double *u) {
   oracle_t *o = h;
-  int64_t m = o->n_cells * o->n * 5;
+  int64_t m = o->n_cells * o->kf;
   double *r = malloc(sizeof(double) * m), *u0 = malloc(sizeof(double) * m), *un = malloc(sizeof(double) * m);
   memcpy(u0, u, sizeof(double) * m);
 #define EULER_NEXT(tt, dst) do { oracle_residual(o, (tt), u, r); \
@@ -1030,6 +1044,10 @@ double oracle_time_step(void *h, const double *u, double dt_guess, int rk_order)
     {1.392, 0.464, 0.235, 0.145, 0.100, 0.073, 0.056, 0.045, 0.037}};
   oracle_t *o = h;
   double min_dt = 1e100;
+  if (o->scheme == 9) {
+    double dt9 = cfl[rk_order][o->degree] * dgm_min_dt(o, u);
+    return dt_guess < dt9 ? dt_guess : dt9;
+  }
   for (int64_t c = 0; c < o->n_cells; ++c) {
     double vmax = 1e-5;
     for (int a = 0; a < o->n; ++a) {
@@ -1562,4 +1580,234 @@ void oracle_riemann_flux(int riemann, int bc_kind, const double *frame9, const d
 void oracle_riemann_1d(int riemann, const double *pl, const double *pr, double *f) {
   prim_t l = {pl[0], pl[1], pl[2], pl[3], pl[4]}, r = {pr[0], pr[1], pr[2], pr[3], pr[4]};
   solve_1d(riemann, &l, &r, f);
+}
+
+
+/* ---- dg::General on Projection<Scalar, 3, P, 5> ------------------------------------------------- */
+/* spatial/dg/general.hpp:58-89 (+ boundary loops :92-200), polynomial/projection.hpp:67-176, basis/linear.hpp:87-141,
+   integrator/legendre.hpp:20-80, integrator/hexahedron.hpp:55-135, integrator/quadrangle.hpp:66-110.
+   Column: [cell][mode][component] (expansion.hpp:83-90 on the column-major K x M Coeff). */
+typedef struct {
+  int m;                    /* modes per component */
+  double gx[MAXQ], gw[MAXQ];
+  double *xyz, *wgt;        /* [cell][n][3], [cell][n]: Gauss points and global weights */
+  modal_basis_t *basis;     /* [cell] */
+  double *fxyz, *fw;        /* [face][fq][3], [face][fq] */
+  frame_t *frame;           /* [face][fq] */
+} dgm_t;
+
+static void legendre_rule(int q, double *x, double *w) { /* integrator/legendre.hpp:50-73 */
+  if (q == 3) {
+    x[0] = -sqrt(0.6); x[1] = 0; x[2] = sqrt(0.6);
+    w[0] = 5.0 / 9.0; w[1] = 8.0 / 9.0; w[2] = 5.0 / 9.0;
+  } else {
+    double a = sqrt((3 + 2 * sqrt(1.2)) / 7), b = sqrt((3 - 2 * sqrt(1.2)) / 7);
+    x[0] = -a; x[1] = -b; x[2] = b; x[3] = a;
+    w[0] = w[3] = (18 - sqrt(30.0)) / 36; w[1] = w[2] = (18 + sqrt(30.0)) / 36;
+  }
+}
+static void dgm_basis_build(const oracle_t *o, const dgm_t *g, int64_t c, const double *ctr, modal_basis_t *b) {
+  int n = o->n, m = g->m;
+  double A[MAXM][MAXM] = {{0}}, S[MAXM][MAXM] = {{0}};
+  memcpy(b->center, ctr, sizeof b->center);
+  for (int a = 0; a < n; ++a) {
+    double d[3], t[MAXM], w = g->wgt[c * n + a];
+    for (int k = 0; k < 3; ++k) d[k] = g->xyz[(c * n + a) * 3 + k] - ctr[k];
+    taylor_values(o->degree, d, t);
+    for (int i = 0; i < m; ++i) for (int j = 0; j < m; ++j) A[i][j] += t[i] * t[j] * w;
+  }
+  for (int i = 0; i < m; ++i) S[i][i] = 1;
+  S[0][0] = 1 / sqrt(A[0][0]);
+  for (int i = 1; i < m; ++i) {
+    for (int j = 0; j < i; ++j) {
+      double temp = 0;
+      for (int k = 0; k <= j; ++k) temp += S[j][k] * A[k][i];
+      for (int l = 0; l <= j; ++l) S[i][l] -= temp * S[j][l];
+    }
+    double norm_sq = 0;
+    for (int j = 0; j <= i; ++j) {
+      double sum = 0, sij = S[i][j];
+      for (int k = 0; k < j; ++k) sum += 2 * S[i][k] * A[k][j];
+      norm_sq += sij * (sij * A[j][j] + sum);
+    }
+    double nrm = sqrt(norm_sq);
+    for (int j = 0; j < m; ++j) S[i][j] /= nrm;
+  }
+  memcpy(b->s, S, sizeof S);
+}
+static void dgm_setup(oracle_t *o, const double *nodes, const int64_t *cn) {
+  dgm_t *g = calloc(1, sizeof *g);
+  int q = o->q, n = o->n, fq = q * q;
+  int64_t nc = o->n_cells;
+  o->dgm = g;
+  g->m = taylor_count(o->degree);
+  o->kf = 5 * g->m;
+  legendre_rule(q, g->gx, g->gw);
+  g->xyz = malloc(sizeof(double) * nc * n * 3); g->wgt = malloc(sizeof(double) * nc * n);
+  g->basis = malloc(sizeof(modal_basis_t) * nc);
+  for (int64_t c = 0; c < nc; ++c) {
+    double ctr[3] = {0, 0, 0};
+    for (int v = 0; v < 8; ++v) for (int k = 0; k < 3; ++k) ctr[k] += nodes[cn[c * 8 + v] * 3 + k] / 8;
+    for (int a = 0; a < n; ++a) {
+      int ijk[3] = {a / fq, (a / q) % q, a % q};
+      double loc[3] = {g->gx[ijk[0]], g->gx[ijk[1]], g->gx[ijk[2]]}, X[3] = {0, 0, 0}, J[3][3] = {{0}};
+      for (int v = 0; v < 8; ++v) {
+        const double *P = &nodes[cn[c * 8 + v] * 3];
+        double fx = 1 + VERT[v][0] * loc[0], fy = 1 + VERT[v][1] * loc[1], fz = 1 + VERT[v][2] * loc[2];
+        double shape = fx * fy * fz / 8;
+        double gr[3] = {VERT[v][0] * (fy * fz / 8), VERT[v][1] * (fz * fx / 8), VERT[v][2] * (fx * fy / 8)};
+        for (int k = 0; k < 3; ++k) { X[k] += shape * P[k]; for (int d = 0; d < 3; ++d) J[d][k] += gr[d] * P[k]; }
+      }
+      double c0[3];
+      cross(J[1], J[2], c0);
+      double det = J[0][0] * c0[0] + J[0][1] * c0[1] + J[0][2] * c0[2];
+      memcpy(&g->xyz[(c * n + a) * 3], X, sizeof X);
+      g->wgt[c * n + a] = g->gw[ijk[0]] * g->gw[ijk[1]] * g->gw[ijk[2]] * det;
+    }
+    dgm_basis_build(o, g, c, ctr, &g->basis[c]);
+  }
+  int64_t nf = o->n_faces;
+  g->fxyz = malloc(sizeof(double) * nf * fq * 3); g->fw = malloc(sizeof(double) * nf * fq);
+  g->frame = malloc(sizeof(frame_t) * nf * fq);
+  for (int64_t f = 0; f < nf; ++f) {
+    /* the holder's local face: the one whose four nodes are the face's (h_dir and the sign of h_scale name it) */
+    int d = o->h_dir[f], plus = o->h_scale[f * fq] > 0;
+    int lf = d == 0 ? (plus ? 2 : 4) : d == 1 ? (plus ? 3 : 1) : (plus ? 5 : 0);
+    const double *P[4];
+    for (int mm = 0; mm < 4; ++mm) P[mm] = &nodes[cn[o->holder[f] * 8 + FACE_NODES[lf][mm]] * 3];
+    for (int ia = 0; ia < q; ++ia) for (int ib = 0; ib < q; ++ib) {
+      int p = ia * q + ib;
+      double a = g->gx[ia], b = g->gx[ib], X[3] = {0, 0, 0}, Ja[3] = {0, 0, 0}, Jb[3] = {0, 0, 0};
+      for (int mm = 0; mm < 4; ++mm) {
+        double fa = (1 + QUAD[mm][0] * a), fb = (1 + QUAD[mm][1] * b);
+        for (int k = 0; k < 3; ++k) {
+          X[k] += fa * fb / 4 * P[mm][k];
+          Ja[k] += QUAD[mm][0] * (fb / 4) * P[mm][k];
+          Jb[k] += QUAD[mm][1] * (fa / 4) * P[mm][k];
+        }
+      }
+      memcpy(&g->fxyz[(f * fq + p) * 3], X, sizeof X);
+      frame_t *fr = &g->frame[f * fq + p];
+      double nn[3]; cross(Ja, Jb, nn);
+      double len = norm3(nn), la = norm3(Ja);
+      for (int k = 0; k < 3; ++k) { fr->a[k] = nn[k] / len; fr->b[k] = Ja[k] / la; }
+      cross(fr->a, fr->b, fr->c);
+      double aa = Ja[0] * Ja[0] + Ja[1] * Ja[1] + Ja[2] * Ja[2], bb = Jb[0] * Jb[0] + Jb[1] * Jb[1] + Jb[2] * Jb[2];
+      double ab = Ja[0] * Jb[0] + Ja[1] * Jb[1] + Ja[2] * Jb[2];
+      g->fw[f * fq + p] = g->gw[ia] * g->gw[ib] * sqrt(aa * bb - ab * ab);
+    }
+  }
+}
+static void dgm_free(oracle_t *o) {
+  dgm_t *g = o->dgm;
+  if (!g) return;
+  free(g->xyz); free(g->wgt); free(g->basis); free(g->fxyz); free(g->fw); free(g->frame); free(g);
+  o->dgm = NULL;
+}
+static void dgm_value(const oracle_t *o, const dgm_t *g, int64_t c, const double *u, const double *x, double *phi,
+    double *val) { /* Projection::GlobalToValue (projection.hpp:99-104) */
+  modal_basis_values(o, &g->basis[c], x, phi);
+  for (int k = 0; k < 5; ++k) {
+    double v = 0;
+    for (int i = 0; i < g->m; ++i) v += u[(c * g->m + i) * 5 + k] * phi[i];
+    val[k] = v;
+  }
+}
+/* OrthoNormal::GetGradValue (basis/linear.hpp:131-135, basis/taylor.hpp:374-470): grad[mode][xyz] */
+static void dgm_basis_gradients(const oracle_t *o, const modal_basis_t *b, const double *xg, double grad[MAXM][3]) {
+  int m = taylor_count(o->degree);
+  double x = xg[0] - b->center[0], y = xg[1] - b->center[1], z = xg[2] - b->center[2];
+  double tg[MAXM][3] = {{0}};
+  tg[1][0] = 1; tg[2][1] = 1; tg[3][2] = 1;
+  tg[4][0] = 2 * x; tg[5][0] = y; tg[5][1] = x; tg[6][0] = z; tg[6][2] = x;
+  tg[7][1] = 2 * y; tg[8][1] = z; tg[8][2] = y; tg[9][2] = 2 * z;
+  if (m == 20) {
+    double xx = x * x, xy = x * y, xz = x * z, yy = y * y, yz = y * z, zz = z * z;
+    tg[10][0] = 3 * xx;
+    tg[11][0] = 2 * xy; tg[11][1] = xx;
+    tg[12][0] = 2 * xz; tg[12][2] = xx;
+    tg[13][0] = yy; tg[13][1] = 2 * xy;
+    tg[14][0] = yz; tg[14][1] = xz; tg[14][2] = xy;
+    tg[15][0] = zz; tg[15][2] = 2 * xz;
+    tg[16][1] = 3 * yy;
+    tg[17][1] = 2 * yz; tg[17][2] = yy;
+    tg[18][1] = zz; tg[18][2] = 2 * yz;
+    tg[19][2] = 3 * zz;
+  }
+  for (int i = 0; i < m; ++i) for (int d = 0; d < 3; ++d) {
+    double v = 0;
+    for (int j = 0; j <= i; ++j) v += b->s[i][j] * tg[j][d];
+    grad[i][d] = v;
+  }
+}
+static void dgm_residual(oracle_t *o, double t, const double *u, double *res) {
+  dgm_t *g = o->dgm;
+  int n = o->n, fq = o->q * o->q, m = g->m;
+  int64_t nc = o->n_cells;
+  memset(res, 0, sizeof(double) * nc * m * 5);
+  for (int64_t c = 0; c < nc; ++c)
+    for (int a = 0; a < n; ++a) { /* dg/general.hpp:58-69 */
+      double phi[MAXM], val[5], F[5][3], grad[MAXM][3];
+      const double *x = &g->xyz[(c * n + a) * 3];
+      dgm_value(o, g, c, u, x, phi, val);
+      flux_matrix(val, F);
+      dgm_basis_gradients(o, &g->basis[c], x, grad);
+      double w = g->wgt[c * n + a];
+      for (int i = 0; i < m; ++i) for (int k = 0; k < 5; ++k)
+        res[(c * m + i) * 5 + k] += (F[k][0] * w) * grad[i][0] + (F[k][1] * w) * grad[i][1] + (F[k][2] * w) * grad[i][2];
+    }
+  for (int64_t f = 0; f < o->n_faces; ++f) {
+    int64_t ch = o->holder[f], cs = o->sharer[f];
+    for (int p = 0; p < fq; ++p) {
+      const frame_t *fr = &g->frame[f * fq + p];
+      const double *x = &g->fxyz[(f * fq + p) * 3];
+      double ph[MAXM], ps[MAXM], uh[5], us[5], fu[5];
+      dgm_value(o, g, ch, u, x, ph, uh);
+      if (cs >= 0) { /* dg/general.hpp:70-89 */
+        dgm_value(o, g, cs, u, x, ps, us);
+        flux_upwind(o->riemann, fr, uh, us, fu);
+      } else { /* dg/general.hpp:92-200 */
+        int tag = o->tag[f], kind = o->bc_kind[tag];
+        double given[5] = {0, 0, 0, 0, 0};
+        if (kind == 6) continue; /* not overridden: fem.hpp:382-383 */
+        if (kind >= 2) eval_field(o->field_kind[tag], o->field_prm[tag], x, t, given);
+        boundary_flux(o->riemann, kind, fr, uh, given, fu);
+      }
+      double w = g->fw[f * fq + p];
+      for (int k = 0; k < 5; ++k) fu[k] *= -w;
+      for (int i = 0; i < m; ++i) for (int k = 0; k < 5; ++k) res[(ch * m + i) * 5 + k] += fu[k] * ph[i];
+      if (cs >= 0) for (int i = 0; i < m; ++i) for (int k = 0; k < 5; ++k) res[(cs * m + i) * 5 + k] += -fu[k] * ps[i];
+    }
+  }
+}
+static double dgm_min_dt(oracle_t *o, const double *u) { /* fem.hpp:417-432 with Cell::N = M quadrature points */
+  dgm_t *g = o->dgm;
+  double min_dt = 1e100;
+  for (int64_t c = 0; c < o->n_cells; ++c) {
+    double vmax = 1e-5;
+    for (int a = 0; a < g->m; ++a) {
+      double phi[MAXM], val[5];
+      dgm_value(o, g, c, u, &g->xyz[(c * o->n + a) * 3], phi, val);
+      prim_t q = cons_to_prim(val);
+      double cs = sound_speed(q.rho, q.p), v = sqrt(q.u * q.u + q.v * q.v + q.w * q.w);
+      double s = cs + v > cs - v ? cs + v : cs - v;
+      if (s > vmax) vmax = s;
+    }
+    double d = o->length[c] / vmax;
+    if (d < min_dt) min_dt = d;
+  }
+  return min_dt;
+}
+static void dgm_approximate(oracle_t *o, int field_kind, const double *prm, double *column) { /* projection.hpp:28-43 */
+  dgm_t *g = o->dgm;
+  int n = o->n, m = g->m;
+  memset(column, 0, sizeof(double) * o->n_cells * m * 5);
+  for (int64_t c = 0; c < o->n_cells; ++c)
+    for (int a = 0; a < n; ++a) {
+      double phi[MAXM], val[5];
+      const double *x = &g->xyz[(c * n + a) * 3];
+      eval_field(field_kind, prm, x, 0.0, val);
+      modal_basis_values(o, &g->basis[c], x, phi);
+      for (int i = 0; i < m; ++i) for (int k = 0; k < 5; ++k) column[(c * m + i) * 5 + k] += val[k] * phi[i] * g->wgt[c * n + a];
+    }
 }

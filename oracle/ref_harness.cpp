@@ -44,6 +44,9 @@
 #include "mini/coordinate/quadrangle.hpp"
 #include "mini/integrator/hexahedron.hpp"
 #include "mini/integrator/lobatto.hpp"
+#include "mini/integrator/legendre.hpp"
+#include "mini/polynomial/projection.hpp"
+#include "mini/spatial/dg/general.hpp"
 #include "mini/integrator/quadrangle.hpp"
 #include "mini/limiter/average.hpp"
 // limiter/majority.hpp:27 names `Scalar` unqualified; the drivers define that alias at global scope before
@@ -139,6 +142,22 @@ struct GlobalMesh {
 template <class Poly>
 struct OracleFace;
 
+// What a polynomial type does not say itself: the concrete cell integrator and the 1-D rule of the face integrators.
+// The nodal Hexahedron carries both; the modal Projection (polynomial/projection.hpp) only knows the abstract
+// integrator::Cell, its rules come from the driver (demo/euler/sourceless.hpp:28-33: Legendre under DGFEM).
+template <class Poly>
+struct PolyTraits {
+  using CellIntegrator = typename Poly::Integrator;
+  using Gx = typename Poly::IntegratorX;
+};
+using ModalDgRule = mini::integrator::Legendre<double, REF_DEGREE + 1>;
+using ModalDgPoly = mini::polynomial::Projection<double, 3, REF_DEGREE, 5>;
+template <>
+struct PolyTraits<ModalDgPoly> {
+  using CellIntegrator = mini::integrator::Hexahedron<ModalDgRule, ModalDgRule, ModalDgRule>;
+  using Gx = ModalDgRule;
+};
+
 template <class Poly>
 struct OracleCell {
   using Polynomial = Poly;
@@ -161,7 +180,7 @@ struct OracleCell {
   std::vector<Face *> boundary_faces_;
 
   std::unique_ptr<mini::coordinate::Hexahedron8<Scalar>> coordinate_ptr_;
-  std::unique_ptr<typename Polynomial::Integrator> integrator_ptr_;
+  std::unique_ptr<typename PolyTraits<Poly>::CellIntegrator> integrator_ptr_;
   std::unique_ptr<Polynomial> polynomial_ptr_;
   Scalar length_;
   Int metis_id{-1};
@@ -176,7 +195,7 @@ struct OracleCell {
     };
     coordinate_ptr_.reset(new mini::coordinate::Hexahedron8<Scalar>{
         G(0), G(1), G(2), G(3), G(4), G(5), G(6), G(7)});
-    integrator_ptr_ = std::make_unique<typename Polynomial::Integrator>(*coordinate_ptr_);
+    integrator_ptr_ = std::make_unique<typename PolyTraits<Poly>::CellIntegrator>(*coordinate_ptr_);
     polynomial_ptr_ = std::make_unique<Polynomial>(*integrator_ptr_);
     length_ = std::cbrt(volume()) * 0.5;  // part.hpp:230
   }
@@ -212,7 +231,7 @@ struct OracleFace {
   using Coordinate = mini::coordinate::Face<Scalar, 3>;
   using Cell = OracleCell<Poly>;
   using Global = typename Cell::Global;
-  using Gx = typename Poly::IntegratorX;
+  using Gx = typename PolyTraits<Poly>::Gx;
 
   std::unique_ptr<mini::coordinate::Quadrangle4<Scalar, 3>> coordinate_ptr_;
   std::unique_ptr<mini::integrator::Quadrangle<3, Gx, Gx>> integrator_ptr_;
@@ -592,7 +611,7 @@ template <class Spatial> struct LimiterOf<Spatial, true> {
 template <class Spatial>
 struct SolverImpl : SolverBase {
   using Part = typename Spatial::Part;   // OraclePart<Poly>, or OraclePart<Extrapolation<Poly>> under a limiter
-  static constexpr bool kLimited = mini::polynomial::Modal<typename Part::Polynomial>;
+  static constexpr bool kLimited = requires(Spatial &sp) { sp.limiter_ptr(); };
   using Limiter = typename LimiterOf<Spatial, kLimited>::type;
   GlobalMesh mesh;
   std::unique_ptr<InProcessComm> comm;
@@ -726,7 +745,7 @@ struct SolverImpl : SolverBase {
     return dt;
   }
   void limiter(int kind) override {
-    if constexpr (!kLimited) {
+    if constexpr (!mini::polynomial::Modal<typename Part::Polynomial>) {
       for (auto &p : parts) {
         if (kind == 0) mini::limiter::average::Reconstruct(p.get());
         else mini::limiter::majority::Reconstruct(p.get());
@@ -800,6 +819,9 @@ using Energy = mini::spatial::EnergyBasedViscosity<Part, IsoViscous<Unrotated>>;
 using EExact = Energy<mini::riemann::euler::Exact<Gas, 3>>;
 using EHllc = Energy<mini::riemann::euler::HartenLaxLeerContact<Gas, 3>>;
 
+// modal DG on the stand-alone Projection polynomial with Gauss-Legendre rules (demo/euler/sourceless.hpp:28-33, 64-66)
+using DgPart = OraclePart<ModalDgPoly>;
+
 // c_next of the next fr::General to be created (fr/general.hpp:218-219); set by ref_pN_set_vincent
 static double g_c_next = 0.0;
 
@@ -834,6 +856,12 @@ static SolverBase *Create(int scheme, int riemann, GlobalMesh &&mesh) {
     switch (riemann) {
     case 0: return new SolverImpl<sp::WithLimiter<sp::fr::Lobatto<ModalPart, RExact>, mini::limiter::weno::Eigen<Cell, RExact>>>(std::move(mesh));
     case 1: return new SolverImpl<sp::WithLimiter<sp::fr::Lobatto<ModalPart, RHllc>, mini::limiter::weno::Eigen<Cell, RHllc>>>(std::move(mesh));
+    }
+  } else if (scheme == 9) {   // dg::General<Part<Projection>, Riemann>
+    switch (riemann) {
+    case 0: return new SolverImpl<sp::dg::General<DgPart, RExact>>(std::move(mesh));
+    case 1: return new SolverImpl<sp::dg::General<DgPart, RHllc>>(std::move(mesh));
+    case 2: return new SolverImpl<sp::dg::General<DgPart, RAusm>>(std::move(mesh));
     }
   } else if (scheme == 8) {   // fr::General with an arbitrary Vincent c on the Navier-Stokes Riemann type
     switch (riemann) {

@@ -40,6 +40,8 @@ class Oracle:
         bt = np.ascontiguousarray(mesh.btags, dtype=np.int32)
         self.n_cells = len(cells)
         self.kfields = 5 * (degree + 1) ** 3
+        if scheme == 9:   # dg::General on the modal Projection polynomial: K x M coefficients per cell
+            self.kfields = 5 * {2: 10, 3: 20}[degree]
         self.h = C.c_void_p(lib().oracle_create(
             C.c_int(degree), C.c_int(scheme), C.c_int(riemann), C.c_int64(len(nodes)), _dp(nodes),
             C.c_int64(len(cells)), cells.ctypes.data_as(C.POINTER(C.c_int64)), C.c_int64(len(bf)),
