@@ -44,7 +44,11 @@ typedef enum {
  * or include/mini/spatial/dg/lobatto.hpp:32-303 (DGSEM). */
 /* MCFD_FR_GENERAL: include/mini/spatial/fr/general.hpp:34-641, the Vincent correction function with the
  * given c_next spread over the whole node line (basis/vincent.hpp:18-102). */
-typedef enum { MCFD_FR_LOBATTO = 0, MCFD_DG_LOBATTO = 1, MCFD_FR_GENERAL = 2 } mcfd_scheme;
+/* MCFD_DG_GENERAL: include/mini/spatial/dg/general.hpp:20-200 on cells whose polynomial is the stand-alone modal
+ * mini::polynomial::Projection<Scalar, 3, P, 5> (include/mini/polynomial/projection.hpp:67-176) with Gauss-Legendre rules
+ * (demo/euler/sourceless.hpp:28-33, 64-66 under DGFEM).  A column then holds K x M modal coefficients per cell
+ * (M = 10 at P = 2, 20 at P = 3), column[cell * 5 M + mode * 5 + component] (polynomial/expansion.hpp:83-90). */
+typedef enum { MCFD_FR_LOBATTO = 0, MCFD_DG_LOBATTO = 1, MCFD_FR_GENERAL = 2, MCFD_DG_GENERAL = 3 } mcfd_scheme;
 
 /* Riemann solver behind mini::riemann::rotated::Euler<...> (include/mini/riemann/rotated/euler.hpp:
  * 153-159): include/mini/riemann/euler/exact.hpp:44-46, hllc.hpp:30-44, ausm.hpp:30-33. */
@@ -190,6 +194,16 @@ int mcfd_get_cell_viscosity(mcfd_ctx *ctx, double *nu);   /* [n_local + n_ghost]
 int mcfd_build_damping_matrices(mcfd_ctx *ctx);
 int mcfd_get_damping_matrices(mcfd_ctx *ctx, double *matrices);   /* [n_local][N][N], row-major */
 int mcfd_update_cell_viscosity(mcfd_ctx *ctx, double time_scale);
+
+/* -- modal polynomial (MCFD_DG_GENERAL contexts) --------------------------------------------------- */
+
+/* Gauss-Legendre points of the local cells, [n_local][Q^3][3], in the order of integrator::Hexahedron
+ * (include/mini/integrator/hexahedron.hpp:66-80): where FiniteElement::Approximate samples its function. */
+int mcfd_get_quadrature_points(const mcfd_ctx *ctx, double *xyz);
+/* Replaces Cell::Approximate -> Projection::Approximate (include/mini/polynomial/projection.hpp:28-43, 170-173): the L2
+ * projection of a function given by its values at those points, values [n_local][Q^3][5], becomes the solution.
+ * For MCFD_DG_GENERAL mcfd_get_boundary_points returns the faces' Gauss points, [face][Q*Q][3]. */
+int mcfd_project(mcfd_ctx *ctx, const double *values);
 
 /* -- temporal::System interface (include/mini/temporal/ode.hpp:17-48) -------------------------- */
 

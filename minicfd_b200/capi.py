@@ -10,7 +10,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libminicfd_b200.so")
 
-FR_LOBATTO, DG_LOBATTO, FR_GENERAL = 0, 1, 2
+FR_LOBATTO, DG_LOBATTO, FR_GENERAL, DG_GENERAL = 0, 1, 2, 3
 EXACT, HLLC, AUSM = 0, 1, 2
 INVISCID, NAVIER_STOKES_DDG, CELL_VISCOSITY_DDG = 0, 1, 2
 (BC_INVISCID_WALL, BC_SUPERSONIC_OUTLET, BC_SUPERSONIC_INLET, BC_SUBSONIC_INLET, BC_SUBSONIC_OUTLET,
@@ -59,6 +59,8 @@ SYMBOLS = {
     "mcfd_build_damping_matrices": (C.c_int, [_P]),
     "mcfd_get_damping_matrices": (C.c_int, [_P, _D]),
     "mcfd_update_cell_viscosity": (C.c_int, [_P, C.c_double]),
+    "mcfd_get_quadrature_points": (C.c_int, [_P, _D]),
+    "mcfd_project": (C.c_int, [_P, _D]),
     "mcfd_set_time_callback": (C.c_int, [_P, TIME_CALLBACK, _P]),
     "mcfd_count_local_cells": (C.c_int64, [_P]),
     "mcfd_cell_data_size": (C.c_int64, [_P]),
@@ -139,6 +141,8 @@ class Context:
         self.degree = degree
         self.q = degree + 1
         self.kfields = 5 * self.q ** 3
+        if scheme == DG_GENERAL:       # K x M modal coefficients per cell
+            self.kfields = 5 * (10 if degree == 2 else 20)
         self.n_local = 0
         self._cb = None
 
@@ -174,6 +178,16 @@ class Context:
         out = np.empty((self.n_local if n_cells is None else n_cells, 5))
         self._check(self.lib.mcfd_get_cell_viscosity(self.h, _dp(out)))
         return out
+
+    def quadrature_points(self):
+        out = np.empty((self.n_local, self.q ** 3, 3))
+        self._check(self.lib.mcfd_get_quadrature_points(self.h, _dp(out)))
+        return out
+
+    def project(self, values):
+        v = np.ascontiguousarray(values, dtype=np.float64)
+        assert v.size == self.n_local * self.q ** 3 * 5
+        self._check(self.lib.mcfd_project(self.h, _dp(v)))
 
     def set_cell_viscosity(self, nu):
         nu = np.ascontiguousarray(nu, dtype=np.float64).reshape(-1, 5)

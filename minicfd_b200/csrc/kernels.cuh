@@ -59,6 +59,7 @@ struct Tables {
   // - and + end of a node line; the lumped Lobatto scheme only has g[0][0] and g[1][Q-1]
   int general;
   double g[2][kMaxQ];
+  double gx[kMaxQ], gw[kMaxQ];         // Gauss-Legendre rule of dg::General (integrator/legendre.hpp:50-73)
   double d1[kMaxQ][kMaxQ];             // l_m'(x_i)  (viscous path: local gradients)
   double d2[kMaxQ][kMaxQ];             // l_m''(x_i) (viscous path: local Hessians)
   int slot_node[kMaxWarps * kMaxSlots];  // node handled by (warp, slot), -1 = idle
@@ -1464,6 +1465,275 @@ __global__ void ProbeStateKernel(double *u, int rows_per_tile, int n_tiles, int 
   if (i >= (size_t)n_tiles * rows_per_tile * kTile) return;
   const int row = (int)((i / kTile) % rows_per_tile);
   u[i] = (row / 5 == col) ? 1.0 : 0.0;
+}
+#endif
+
+// ---- dg::General on the modal Projection polynomial --------------------------------------------
+// spatial/dg/general.hpp:58-200 with polynomial/projection.hpp:67-176 on Gauss-Legendre rules (demo/euler/
+// sourceless.hpp:28-33, 64-66).  State: [tile][mode*5 + comp][lane], M modes per component on the cell's orthonormal
+// basis phi = S taylor(x - centre) (BAS, built with the Legendre rule).  One thread per cell: values come from the
+// Taylor form t = S^T a (TAY, written for every cell, ghosts included, by DgmTaylorCell), the residual is gathered
+// as Taylor moments G_j = sum_q (...) taylor_j / grad taylor_j and turned into modal coefficients by S once.
+struct DgmArgs {
+  const double *u_in, *u0;      // modal coefficients (tiles)
+  double *u_out;
+  const double *tay;            // Taylor coefficients of u_in for every cell
+  const double *geom, *bas, *h2s;
+  const int *nbr;
+  const unsigned char *code, *bkind;
+  const double *bvals;          // [n_bfaces][Q*Q][5] boundary function at the face's Gauss points
+  int cell_begin, cell_end, mode;
+  double dt;
+  const double *dt_dev;
+};
+
+template <int P>
+MCFD_HD void TaylorGradients(const double *d, double (*tg)[3]) {   // basis/taylor.hpp:374-470, per monomial
+  constexpr int M = ModalShape<P>::M;
+  const double x = d[0], y = d[1], z = d[2];
+  for (int j = 0; j < M; ++j) { tg[j][0] = 0; tg[j][1] = 0; tg[j][2] = 0; }
+  tg[1][0] = 1; tg[2][1] = 1; tg[3][2] = 1;
+  tg[4][0] = 2 * x; tg[5][0] = y; tg[5][1] = x; tg[6][0] = z; tg[6][2] = x;
+  tg[7][1] = 2 * y; tg[8][1] = z; tg[8][2] = y; tg[9][2] = 2 * z;
+  if (P == 3) {
+    const double xx = x * x, xy = x * y, xz = x * z, yy = y * y, yz = y * z, zz = z * z;
+    tg[10][0] = 3 * xx;
+    tg[11][0] = 2 * xy; tg[11][1] = xx;
+    tg[12][0] = 2 * xz; tg[12][2] = xx;
+    tg[13][0] = yy; tg[13][1] = 2 * xy;
+    tg[14][0] = yz; tg[14][1] = xz; tg[14][2] = xy;
+    tg[15][0] = zz; tg[15][2] = 2 * xz;
+    tg[16][1] = 3 * yy;
+    tg[17][1] = 2 * yz; tg[17][2] = yy;
+    tg[18][1] = zz; tg[18][2] = 2 * yz;
+    tg[19][2] = 3 * zz;
+  }
+}
+
+// offset from the cell centre of the point with local coordinates (x, e, z), and the metric there
+MCFD_HD Metric DgmPoint(const double *geo, int gs, double x, double e, double z, double *d) {
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    d[a] = geo[(0 + a) * gs] * x + geo[(3 + a) * gs] * e + geo[(6 + a) * gs] * z + geo[(9 + a) * gs] * (x * e)
+         + geo[(12 + a) * gs] * (e * z) + geo[(15 + a) * gs] * (z * x) + geo[(18 + a) * gs] * (x * e * z);
+  }
+  return ComputeMetric(geo, gs, x, e, z);
+}
+
+// t = S^T a for the five components of one cell (Projection::GetCoeffOnTaylorBasis, projection.hpp:117-119)
+template <int Q>
+MCFD_HD void DgmTaylorCell(const double *u, const double *bas, double *tay, int tile, int tl) {
+  constexpr int P = Q - 1, M = ModalShape<P>::M, kBasRows = ModalShape<P>::kBasRows;
+  const double *S = bas + ((size_t)tile * kBasRows + ModalShape<P>::kSOffset) * kTile + tl;
+  for (int k = 0; k < 5; ++k) {
+    double a[M], t[M];
+    for (int i = 0; i < M; ++i) a[i] = u[((size_t)tile * 5 * M + i * 5 + k) * kTile + tl];
+    ModalToTaylor<M>(S, kTile, a, t);
+    for (int i = 0; i < M; ++i) tay[((size_t)tile * 5 * M + i * 5 + k) * kTile + tl] = t[i];
+  }
+}
+
+template <int P>
+MCFD_HD void DgmValue(const double *t, size_t stride, const double *d, double *val) {   // sum_j t_j taylor_j(d)
+  constexpr int M = ModalShape<P>::M;
+  double tv[M];
+  TaylorValues<P>(d, tv);
+#pragma unroll
+  for (int k = 0; k < 5; ++k) val[k] = 0;
+  for (int j = 0; j < M; ++j) {
+#pragma unroll
+    for (int k = 0; k < 5; ++k) val[k] = fma(t[(size_t)(j * 5 + k) * stride], tv[j], val[k]);
+  }
+}
+
+// One cell: residual (dg/general.hpp:58-89 + the boundary loops) and RK update of its modal coefficients.
+template <int Q, int kRiemann>
+MCFD_HD void DgmStageCell(const DgmArgs &p, int tile, int tl) {
+  constexpr int P = Q - 1, M = ModalShape<P>::M, kBasRows = ModalShape<P>::kBasRows, FQ = Q * Q;
+  const double *geo = p.geom + (size_t)tile * kGeomRows * kTile + tl;
+  const double *mine = p.tay + (size_t)tile * 5 * M * kTile + tl;
+  double G[M][5];
+  for (int j = 0; j < M; ++j) for (int k = 0; k < 5; ++k) G[j][k] = 0;
+  for (int i = 0; i < Q; ++i) for (int j2 = 0; j2 < Q; ++j2) for (int k2 = 0; k2 < Q; ++k2) {   // volume
+    double d[3], u[5];
+    const Metric mt = DgmPoint(geo, kTile, c_tab.gx[i], c_tab.gx[j2], c_tab.gx[k2], d);
+    const double w = c_tab.gw[i] * c_tab.gw[j2] * c_tab.gw[k2] * mt.det;
+    DgmValue<P>(mine, kTile, d, u);
+    const Prim q = ConsToPrim(u[0], u[1], u[2], u[3], u[4]);
+    const double h0 = u[4] + q.p, vel[3] = {q.u, q.v, q.w};
+    double fx[3][5];
+#pragma unroll
+    for (int x = 0; x < 3; ++x) {
+      fx[x][0] = u[1 + x];
+      fx[x][1] = u[1] * vel[x]; fx[x][2] = u[2] * vel[x]; fx[x][3] = u[3] * vel[x];
+      fx[x][1 + x] += q.p;
+      fx[x][4] = h0 * vel[x];
+#pragma unroll
+      for (int c = 0; c < 5; ++c) fx[x][c] *= w;
+    }
+    double tg[M][3];
+    TaylorGradients<P>(d, tg);
+    for (int j = 1; j < M; ++j) {
+#pragma unroll
+      for (int c = 0; c < 5; ++c) G[j][c] += fx[0][c] * tg[j][0] + fx[1][c] * tg[j][1] + fx[2][c] * tg[j][2];
+    }
+  }
+  for (int f = 0; f < 6; ++f) {   // faces
+    const int nb = p.nbr[((size_t)tile * 6 + f) * kTile + tl];
+    const int cd = p.code[((size_t)tile * 6 + f) * kTile + tl];
+    const int dir = (f == 2 || f == 4) ? 0 : ((f == 1 || f == 3) ? 1 : 2);
+    const double sgn = (f == 2 || f == 3 || f == 5) ? 1.0 : -1.0;
+    const bool holder = (cd & 64) != 0;
+    double off[3] = {0, 0, 0};
+    const double *theirs = mine;
+    if (nb >= 0) {
+      const double *hv = p.h2s + ((size_t)tile * 18 + f * 3) * kTile + tl;
+      const double sg = holder ? 1.0 : -1.0;
+      off[0] = sg * hv[0]; off[1] = sg * hv[kTile]; off[2] = sg * hv[2 * kTile];
+      theirs = p.tay + (size_t)(nb >> 5) * 5 * M * kTile + (nb & 31);
+    }
+    for (int ia = 0; ia < Q; ++ia) for (int ib = 0; ib < Q; ++ib) {
+      // local coordinates: +-1 in `dir`, the Gauss points in the other two (in increasing axis order)
+      const double a = c_tab.gx[ia], b = c_tab.gx[ib];
+      const double x = dir == 0 ? sgn : a, e = dir == 1 ? sgn : (dir == 0 ? a : b), z = dir == 2 ? sgn : b;
+      double d[3], u[5], fl[5];
+      const Metric mt = DgmPoint(geo, kTile, x, e, z, d);
+      const double nx = mt.s[dir][0], ny = mt.s[dir][1], nz = mt.s[dir][2];
+      const double n2 = nx * nx + ny * ny + nz * nz;
+      const double inv_area = Rsqrt(n2), area = n2 * inv_area;
+      const double w = c_tab.gw[ia] * c_tab.gw[ib] * area;
+      DgmValue<P>(mine, kTile, d, u);
+      double out_sign = 1.0;       // flux along MY outward normal = out_sign * (flux in the holder's frame)
+      if (nb >= 0) {
+        const double dn[3] = {d[0] - off[0], d[1] - off[1], d[2] - off[2]};
+        double v[5], ul[5], ur[5];
+        DgmValue<P>(theirs, kTile, dn, v);
+        const double hs = (holder ? sgn : -sgn) * inv_area;
+#pragma unroll
+        for (int c = 0; c < 5; ++c) { ul[c] = holder ? u[c] : v[c]; ur[c] = holder ? v[c] : u[c]; }
+        FluxUpwind<kRiemann>(ul, ur, hs * nx, hs * ny, hs * nz, fl);
+        if (!holder) out_sign = -1.0;
+      } else {
+        const int bf = -1 - nb;
+        const int kind = p.bkind[bf];
+        if (kind == kBcNoSlip) continue;     // dg::General does not override AddFluxOnNoSlipWalls (fem.hpp:382-383)
+        const double inv = sgn * inv_area;
+        State5 ui, given;
+        const double *gv = p.bvals + ((size_t)bf * FQ + ia * Q + ib) * 5;
+#pragma unroll
+        for (int c = 0; c < 5; ++c) { ui.v[c] = u[c]; given.v[c] = gv[c]; }
+        const State5 r = BoundaryFluxOutOfLine<kRiemann>(kind, ui, given, inv * nx, inv * ny, inv * nz);
+#pragma unroll
+        for (int c = 0; c < 5; ++c) fl[c] = r.v[c];
+      }
+      double tv[M];
+      TaylorValues<P>(d, tv);
+      const double ws = -w * out_sign;
+      for (int j = 0; j < M; ++j) {
+#pragma unroll
+        for (int c = 0; c < 5; ++c) G[j][c] = fma(ws * fl[c], tv[j], G[j][c]);
+      }
+    }
+  }
+  // residual on the orthonormal basis: R_m = sum_{j <= m} S[m][j] G_j; then the RK update (rk.hpp:16-49)
+  const double *S = p.bas + ((size_t)tile * kBasRows + ModalShape<P>::kSOffset) * kTile + tl;
+  const double dt = p.dt_dev ? *p.dt_dev : p.dt;
+  int row = 0;
+  for (int m = 0; m < M; ++m) {
+    double r[5] = {0, 0, 0, 0, 0};
+    for (int j = 0; j <= m; ++j) {
+      const double s = S[(size_t)(row + j) * kTile];
+#pragma unroll
+      for (int c = 0; c < 5; ++c) r[c] = fma(s, G[j][c], r[c]);
+    }
+    row += m + 1;
+#pragma unroll
+    for (int c = 0; c < 5; ++c) {
+      const size_t at = ((size_t)tile * 5 * M + m * 5 + c) * kTile + tl;
+      const double u = p.u_in[at], u0 = p.mode >= kModeRk3b ? p.u0[at] : u, res = r[c];
+      double val;
+      switch (p.mode) {
+      case kModeResidual: val = res; break;
+      case kModeEuler: val = u + res * dt; break;
+      case kModeRk3b: val = (u0 * 3 + (u + res * dt)) * 0.25; break;
+      case kModeRk3c: val = ((u + res * dt) * 2 + u0) / 3; break;
+      default: val = ((u + res * dt) + u0) * 0.5; break;
+      }
+      p.u_out[at] = val;
+    }
+  }
+}
+
+// FiniteElement::GetTimeStep on a modal cell: Cell::N = M, so the first M Gauss points are sampled (fem.hpp:419-426)
+template <int Q>
+MCFD_HD double DgmCellSpeed(const double *tay, const double *geom, int tile, int tl) {
+  constexpr int P = Q - 1, M = ModalShape<P>::M;
+  const double *geo = geom + (size_t)tile * kGeomRows * kTile + tl;
+  const double *mine = tay + (size_t)tile * 5 * M * kTile + tl;
+  double vmax = 1e-5;
+  for (int n = 0; n < M; ++n) {
+    const int i = n / (Q * Q), j = (n / Q) % Q, k = n % Q;
+    double d[3], u[5];
+    DgmPoint(geo, kTile, c_tab.gx[i], c_tab.gx[j], c_tab.gx[k], d);
+    DgmValue<P>(mine, kTile, d, u);
+    const Prim q = ConsToPrim(u[0], u[1], u[2], u[3], u[4]);
+    const double c = SoundSpeed(q.rho, q.p), v = sqrt(q.u * q.u + q.v * q.v + q.w * q.w);
+    vmax = fmax(vmax, fmax(c + v, c - v));
+  }
+  return vmax;
+}
+
+// Projection::Approximate (projection.hpp:28-43) from the function's values at the cell's Gauss points,
+// values [cell][Q^3][5] in the reference's column order; writes the modal coefficients of one cell
+template <int Q>
+MCFD_HD void DgmProjectCell(const double *values, const double *geom, const double *bas, double *u, int cell) {
+  constexpr int P = Q - 1, M = ModalShape<P>::M, N = Q * Q * Q, kBasRows = ModalShape<P>::kBasRows;
+  const int tile = cell >> 5, tl = cell & 31;
+  const double *geo = geom + (size_t)tile * kGeomRows * kTile + tl;
+  const double *S = bas + ((size_t)tile * kBasRows + ModalShape<P>::kSOffset) * kTile + tl;
+  for (int k = 0; k < 5; ++k) {
+    double g[M], a[M];
+    for (int j = 0; j < M; ++j) g[j] = 0;
+    for (int n = 0; n < N; ++n) {
+      const int i = n / (Q * Q), j2 = (n / Q) % Q, k2 = n % Q;
+      double d[3], tv[M];
+      const Metric mt = DgmPoint(geo, kTile, c_tab.gx[i], c_tab.gx[j2], c_tab.gx[k2], d);
+      const double wf = c_tab.gw[i] * c_tab.gw[j2] * c_tab.gw[k2] * mt.det * values[((size_t)cell * N + n) * 5 + k];
+      TaylorValues<P>(d, tv);
+      for (int j = 0; j < M; ++j) g[j] = fma(tv[j], wf, g[j]);
+    }
+    MomentsToModal<M>(S, kTile, g, a);
+    for (int j = 0; j < M; ++j) u[((size_t)tile * 5 * M + j * 5 + k) * kTile + tl] = a[j];
+  }
+}
+
+#ifdef __CUDACC__
+template <int Q, int kRiemann>
+__global__ void __launch_bounds__(kTile) DgmStageKernel(DgmArgs p, int tile_begin) {
+  const int tile = tile_begin + blockIdx.x, cell = tile * kTile + threadIdx.x;
+  if (cell < p.cell_begin || cell >= p.cell_end) return;
+  DgmStageCell<Q, kRiemann>(p, tile, threadIdx.x);
+}
+template <int Q>
+__global__ void __launch_bounds__(kTile) DgmTaylorKernel(const double *u, const double *bas, double *tay, int tile_begin,
+    int cell_begin, int cell_end) {
+  const int tile = tile_begin + blockIdx.x, cell = tile * kTile + threadIdx.x;
+  if (cell < cell_begin || cell >= cell_end) return;
+  DgmTaylorCell<Q>(u, bas, tay, tile, threadIdx.x);
+}
+template <int Q>
+__global__ void __launch_bounds__(kTile) DgmTimeStepKernel(const double *tay, const double *geom, const double *length,
+    int n_local, unsigned long long *result) {
+  const int tile = blockIdx.x, cell = tile * kTile + threadIdx.x;
+  double dt = 1e100;
+  if (cell < n_local) dt = length[cell] / DgmCellSpeed<Q>(tay, geom, tile, threadIdx.x);
+  for (int o = 16; o > 0; o >>= 1) dt = fmin(dt, __shfl_xor_sync(0xffffffffu, dt, o));
+  if (threadIdx.x == 0) atomicMin(result, (unsigned long long)__double_as_longlong(dt));
+}
+template <int Q>
+__global__ void DgmProjectKernel(const double *values, const double *geom, const double *bas, double *u, int n_local) {
+  const int cell = blockIdx.x * blockDim.x + threadIdx.x;
+  if (cell < n_local) DgmProjectCell<Q>(values, geom, bas, u, cell);
 }
 #endif
 

@@ -199,10 +199,46 @@ int LaunchTrace(mcfd_ctx *ctx, const double *u, int64_t cell_begin, int64_t cell
   return MCFD_OK;
 }
 
+// dg::General on the modal polynomial: Taylor form of the cells [cell_begin, cell_end) of `u`
+int LaunchDgmTaylor(mcfd_ctx *ctx, const double *u, int64_t cell_begin, int64_t cell_end) {
+  if (cell_end <= cell_begin) return MCFD_OK;
+  const int t0 = (int)(cell_begin / kTile), t1 = (int)((cell_end + kTile - 1) / kTile);
+  MCFD_CUDA(ctx, EnsureTables(ctx));
+  if (ctx->q == 3) DgmTaylorKernel<3><<<t1 - t0, kTile, 0, ctx->stream>>>(u, ctx->bas.p, ctx->tay.p, t0, (int)cell_begin, (int)cell_end);
+  else DgmTaylorKernel<4><<<t1 - t0, kTile, 0, ctx->stream>>>(u, ctx->bas.p, ctx->tay.p, t0, (int)cell_begin, (int)cell_end);
+  MCFD_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  return MCFD_OK;
+}
+
+template <int Q>
+cudaError_t LaunchDgmQ(mcfd_ctx *ctx, DgmArgs const &a, int t0, int n_tiles) {
+  switch (ctx->cfg.riemann) {
+  case MCFD_EXACT: DgmStageKernel<Q, kExact><<<n_tiles, kTile, 0, ctx->stream>>>(a, t0); break;
+  case MCFD_HLLC: DgmStageKernel<Q, kHllc><<<n_tiles, kTile, 0, ctx->stream>>>(a, t0); break;
+  default: DgmStageKernel<Q, kAusm><<<n_tiles, kTile, 0, ctx->stream>>>(a, t0); break;
+  }
+  return cudaGetLastError();
+}
+
 // Launch the stage kernel over CTA blocks [block_begin, block_end).
 int LaunchStage(mcfd_ctx *ctx, const double *u_in, const double *u0, double *u_out, int mode,
     double dt, int64_t block_begin, int64_t block_end) {
   if (block_end <= block_begin) return MCFD_OK;
+  if (ctx->cfg.scheme == MCFD_DG_GENERAL) {   // blocks are tiles here
+    DgmArgs d;
+    d.u_in = u_in; d.u0 = u0; d.u_out = u_out; d.tay = ctx->tay.p; d.geom = ctx->geom.p; d.bas = ctx->bas.p;
+    d.h2s = ctx->h2s.p; d.nbr = ctx->nbr.p; d.code = ctx->code.p; d.bkind = ctx->bkind.p; d.bvals = ctx->bvals.p;
+    d.cell_begin = (int)(block_begin * kTile);
+    d.cell_end = (int)std::min<int64_t>(block_end * kTile, ctx->mesh.n_local);
+    d.mode = mode; d.dt = dt; d.dt_dev = ctx->rk_order ? ctx->rk_dt_dev : nullptr;
+    MCFD_CUDA(ctx, EnsureTables(ctx));
+    cudaError_t e = ctx->q == 3 ? LaunchDgmQ<3>(ctx, d, (int)block_begin, (int)(block_end - block_begin))
+                                : LaunchDgmQ<4>(ctx, d, (int)block_begin, (int)(block_end - block_begin));
+    if (e != cudaSuccess) return Fail(ctx, MCFD_ERR_CUDA, std::string("dg::General stage kernel: ") + cudaGetErrorString(e));
+    ctx->launches++;
+    return MCFD_OK;
+  }
   StageArgs a;
   a.u_in = u_in; a.u0 = u0; a.u_out = u_out;
   a.geom = ctx->geom.p; a.nbr = ctx->nbr.p; a.code = ctx->code.p;
@@ -245,7 +281,11 @@ int LaunchConvert(mcfd_ctx *ctx, double *tiles, double *column, const int *cells
   if (n_items == 0) return MCFD_OK;
   int blocks = (int)((n_items + kTile - 1) / kTile);
   cudaError_t e;
-  if (ctx->q == 3) {
+  if (ctx->fields == 50 || ctx->fields == 100) {   // dg::General: 5 x M modal coefficients per cell
+    if (ctx->fields == 50) ConvertKernel<50, kToTiles><<<blocks, 256, (size_t)kTile * 51 * sizeof(double), ctx->stream>>>(tiles, column, cells, (int)n_items);
+    else ConvertKernel<100, kToTiles><<<blocks, 256, (size_t)kTile * 101 * sizeof(double), ctx->stream>>>(tiles, column, cells, (int)n_items);
+    e = cudaGetLastError();
+  } else if (ctx->q == 3) {
     constexpr int F = 135;
     size_t smem = (size_t)kTile * (F + 1) * sizeof(double);
     ConvertKernel<F, kToTiles><<<blocks, 256, smem, ctx->stream>>>(tiles, column, cells, (int)n_items);
@@ -312,8 +352,10 @@ int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
   if (!config || !ctx_out) return Fail(nullptr, MCFD_ERR_ARG, "null argument");
   if (config->degree != 2 && config->degree != 3)
     return Fail(nullptr, MCFD_ERR_ARG, "degree must be 2 or 3");
-  if (config->scheme < MCFD_FR_LOBATTO || config->scheme > MCFD_FR_GENERAL)
+  if (config->scheme < MCFD_FR_LOBATTO || config->scheme > MCFD_DG_GENERAL)
     return Fail(nullptr, MCFD_ERR_ARG, "unknown scheme");
+  if (config->scheme == MCFD_DG_GENERAL && config->diffusion != MCFD_INVISCID)
+    return Fail(nullptr, MCFD_ERR_ARG, "the reference's DG schemes have no diffusive terms");
   if (config->riemann < MCFD_EXACT || config->riemann > MCFD_AUSM)
     return Fail(nullptr, MCFD_ERR_ARG, "unknown Riemann solver");
   if (config->diffusion < MCFD_INVISCID || config->diffusion > MCFD_CELL_VISCOSITY_DDG)
@@ -339,7 +381,8 @@ int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
   ctx->q = config->degree + 1;
   ctx->n_nodes = ctx->q * ctx->q * ctx->q;
   ctx->fields = 5 * ctx->n_nodes;
-  ctx->cpb = (ctx->q == 3) ? kP2Cells : kP3Cells;
+  if (config->scheme == MCFD_DG_GENERAL) ctx->fields = 5 * (ctx->q == 3 ? 10 : 20);   // K x M modal coefficients
+  ctx->cpb = (config->scheme == MCFD_DG_GENERAL) ? kTile : ((ctx->q == 3) ? kP2Cells : kP3Cells);
   ctx->n_warps = (ctx->q == 3) ? (config->diffusion != MCFD_INVISCID ? kP2ViscousWarps : kP2Warps) : kP3Warps;
   ctx->tables = BuildTables(config->degree, config->scheme, ctx->n_warps, kTile / ctx->cpb, config->fr_c_next);
   e = ctx->dt_bits.Alloc(1);
@@ -405,7 +448,15 @@ int mcfd_set_mesh(mcfd_ctx *ctx, int64_t n_nodes, const double *xyz, int64_t n_l
     MCFD_CUDA(ctx, ctx->h2s.Alloc(h2s.size()));
     MCFD_CUDA(ctx, cudaMemcpy(ctx->h2s.p, h2s.data(), h2s.size() * sizeof(double), cudaMemcpyHostToDevice));
   }
-  ctx->bas.Free(); ctx->frames.Free(); ctx->weno_scratch.Free(); ctx->damping.Free(); ctx->energy_viscosity = false;
+  ctx->bas.Free(); ctx->tay.Free(); ctx->frames.Free(); ctx->weno_scratch.Free(); ctx->damping.Free(); ctx->energy_viscosity = false;
+  if (ctx->cfg.scheme == MCFD_DG_GENERAL) {   // Projection's orthonormal bases on the Gauss-Legendre rule
+    const int rows = ctx->q == 3 ? ModalShape<2>::kBasRows : ModalShape<3>::kBasRows;
+    auto bas = ToTiles(ctx->mesh.BuildModalBases(ctx->cfg.degree, true), rows, ctx->n_cells, ctx->n_tiles);
+    MCFD_CUDA(ctx, ctx->bas.Alloc(bas.size()));
+    MCFD_CUDA(ctx, cudaMemcpy(ctx->bas.p, bas.data(), bas.size() * sizeof(double), cudaMemcpyHostToDevice));
+    MCFD_CUDA(ctx, ctx->tay.Alloc(state));
+    MCFD_CUDA(ctx, cudaMemset(ctx->tay.p, 0, state * sizeof(double)));
+  }
   if (ctx->cfg.diffusion != MCFD_INVISCID) {
     MCFD_CUDA(ctx, ctx->grad.Alloc((size_t)ctx->n_tiles * ctx->n_nodes * 15 * kTile));
     MCFD_CUDA(ctx, ctx->hn.Alloc((size_t)ctx->n_tiles * 6 * ctx->q * ctx->q * 15 * kTile));
@@ -550,7 +601,8 @@ int64_t mcfd_count_boundary_faces(const mcfd_ctx *ctx, int32_t tag) {
 
 int mcfd_get_boundary_points(const mcfd_ctx *ctx, int32_t tag, double *xyz) {
   if (!ctx || !ctx->has_mesh || !xyz) return MCFD_ERR_STATE;
-  ctx->mesh.BoundaryPoints(ctx->tables, ctx->cfg.degree, tag, xyz);
+  if (ctx->cfg.scheme == MCFD_DG_GENERAL) ctx->mesh.BoundaryGaussPoints(ctx->tables, ctx->cfg.degree, tag, xyz);
+  else ctx->mesh.BoundaryPoints(ctx->tables, ctx->cfg.degree, tag, xyz);
   return MCFD_OK;
 }
 
@@ -667,6 +719,32 @@ int mcfd_set_cell_viscosity(mcfd_ctx *ctx, int64_t n_cells, const double *nu) {
   return MCFD_OK;
 }
 
+int mcfd_get_quadrature_points(const mcfd_ctx *ctx, double *xyz) {
+  if (!ctx || !ctx->has_mesh || !xyz) return MCFD_ERR_STATE;
+  if (ctx->cfg.scheme != MCFD_DG_GENERAL) return MCFD_ERR_STATE;
+  ctx->mesh.QuadraturePoints(ctx->tables, ctx->cfg.degree, xyz);
+  return MCFD_OK;
+}
+
+int mcfd_project(mcfd_ctx *ctx, const double *values) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (ctx->cfg.scheme != MCFD_DG_GENERAL) return Fail(ctx, MCFD_ERR_STATE, "mcfd_project is for MCFD_DG_GENERAL contexts");
+  if (!values) return Fail(ctx, MCFD_ERR_ARG, "null values");
+  if (ctx->rk_order) return Fail(ctx, MCFD_ERR_STATE, "an RK step is open");
+  const size_t n = (size_t)ctx->mesh.n_local * ctx->n_nodes * 5;
+  DevBuf<double> dv;
+  MCFD_CUDA(ctx, dv.Alloc(n));
+  MCFD_CUDA(ctx, cudaMemcpyAsync(dv.p, values, n * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  MCFD_CUDA(ctx, EnsureTables(ctx));
+  const int nl = (int)ctx->mesh.n_local;
+  if (ctx->q == 3) DgmProjectKernel<3><<<(nl + 63) / 64, 64, 0, ctx->stream>>>(dv.p, ctx->geom.p, ctx->bas.p, ctx->u[ctx->cur].p, nl);
+  else DgmProjectKernel<4><<<(nl + 63) / 64, 64, 0, ctx->stream>>>(dv.p, ctx->geom.p, ctx->bas.p, ctx->u[ctx->cur].p, nl);
+  MCFD_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return MCFD_OK;
+}
+
 int mcfd_set_time_callback(mcfd_ctx *ctx, mcfd_time_callback fn, void *user) {
   if (!ctx) return MCFD_ERR_ARG;
   ctx->time_cb = fn;
@@ -726,6 +804,9 @@ int mcfd_residual(mcfd_ctx *ctx, double t, double *column, double *column_dev) {
   if (ctx->cfg.diffusion != MCFD_INVISCID) {
     if (int s = LaunchTrace(ctx, u, 0, ctx->n_cells)) return s;
   }
+  if (ctx->cfg.scheme == MCFD_DG_GENERAL) {
+    if (int s = LaunchDgmTaylor(ctx, u, 0, ctx->n_cells)) return s;
+  }
   if (int s = LaunchStage(ctx, u, u, ctx->res.p, kModeResidual, 0.0, 0, ctx->total_blocks)) return s;
   if (column_dev) {
     if (int s = LaunchConvert<false>(ctx, ctx->res.p, column_dev, nullptr, ctx->mesh.n_local)) return s;
@@ -775,6 +856,11 @@ int mcfd_rk_stage_inner(mcfd_ctx *ctx, int stage) {
   StageBuffers(ctx, stage, &in, &out, &mode);
   if (in != ctx->rk_in) return Fail(ctx, MCFD_ERR_STATE, "stages must be run in order");
   if (ctx->time_cb) ctx->time_cb(ctx->time_user, mcfd_rk_stage_time(ctx, stage));
+  if (ctx->cfg.scheme == MCFD_DG_GENERAL) {
+    if (int s = LaunchDgmTaylor(ctx, ctx->u[in].p, 0, ctx->mesh.n_local)) return s;
+    if (!ctx->trace_done) MCFD_CUDA(ctx, cudaEventCreateWithFlags(&ctx->trace_done, cudaEventDisableTiming));
+    MCFD_CUDA(ctx, cudaEventRecord(ctx->trace_done, ctx->stream));
+  }
   if (ctx->cfg.diffusion != MCFD_INVISCID) {   // the inner cells' neighbours are all local
     if (int s = LaunchTrace(ctx, ctx->u[in].p, 0, ctx->mesh.n_local)) return s;
     if (!ctx->trace_done) MCFD_CUDA(ctx, cudaEventCreateWithFlags(&ctx->trace_done, cudaEventDisableTiming));
@@ -791,6 +877,10 @@ int mcfd_rk_stage_inter(mcfd_ctx *ctx, int stage) {
   int in, out, mode;
   StageBuffers(ctx, stage, &in, &out, &mode);
   if (in != ctx->rk_in) return Fail(ctx, MCFD_ERR_STATE, "stages must be run in order");
+  if (ctx->cfg.scheme == MCFD_DG_GENERAL) {
+    if (ctx->trace_done) MCFD_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->trace_done, 0));
+    if (int s = LaunchDgmTaylor(ctx, ctx->u[in].p, ctx->mesh.n_local, ctx->n_cells)) return s;
+  }
   if (ctx->cfg.diffusion != MCFD_INVISCID) {   // the ghost cells hold this stage's values by now
     // the inter cells also read the local traces, which mcfd_rk_stage_inner may have launched on another stream
     if (ctx->trace_done) MCFD_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->trace_done, 0));
@@ -834,6 +924,17 @@ int mcfd_time_step_device(mcfd_ctx *ctx, double dt_guess, int rk_order, double *
     ctx->launches += 1;
     return MCFD_OK;
   }
+  if (ctx->cfg.scheme == MCFD_DG_GENERAL) {
+    if (int s = LaunchDgmTaylor(ctx, ctx->u[ctx->cur].p, 0, ctx->mesh.n_local)) return s;
+    TimeStepResetKernel<<<1, 1, 0, ctx->stream>>>(ctx->dt_bits.p);
+    const int nl = (int)ctx->mesh.n_local, tiles = (nl + kTile - 1) / kTile;
+    if (ctx->q == 3) DgmTimeStepKernel<3><<<tiles, kTile, 0, ctx->stream>>>(ctx->tay.p, ctx->geom.p, ctx->length.p, nl, ctx->dt_bits.p);
+    else DgmTimeStepKernel<4><<<tiles, kTile, 0, ctx->stream>>>(ctx->tay.p, ctx->geom.p, ctx->length.p, nl, ctx->dt_bits.p);
+    TimeStepFinishKernel<<<1, 1, 0, ctx->stream>>>(ctx->dt_bits.p, kCfl[rk_order][ctx->cfg.degree], dt_guess, 0, dt_dev);
+    MCFD_CUDA(ctx, cudaGetLastError());
+    ctx->launches += 3;
+    return MCFD_OK;
+  }
   TimeStepResetKernel<<<1, 1, 0, ctx->stream>>>(ctx->dt_bits.p);
   int n = (int)ctx->mesh.n_local, threads = 256, blocks = (n + kTile - 1) / kTile;
   if (ctx->q == 3) TimeStepKernel<3><<<blocks, threads, 0, ctx->stream>>>(ctx->u[ctx->cur].p, ctx->length.p, n, ctx->dt_bits.p);
@@ -865,6 +966,7 @@ int mcfd_rk_step_device(mcfd_ctx *ctx, int order, double t, const double *dt_dev
 int mcfd_limiter_reconstruct(mcfd_ctx *ctx, int kind) {
   if (int s = RequireMesh(ctx)) return s;
   if (kind != 0 && kind != 1) return Fail(ctx, MCFD_ERR_ARG, "limiter kind must be 0 (average) or 1 (majority)");
+  if (ctx->cfg.scheme == MCFD_DG_GENERAL) return Fail(ctx, MCFD_ERR_STATE, "the limiters are built for the nodal expansions");
   if (ctx->rk_order) return Fail(ctx, MCFD_ERR_STATE, "an RK step is open");
   int n = (int)ctx->mesh.n_local, threads = 128, blocks = (n + threads - 1) / threads;
   MCFD_CUDA(ctx, EnsureTables(ctx));
@@ -961,6 +1063,7 @@ int mcfd_eigen_matrices(mcfd_ctx *ctx, int64_t n, const double *conservative, co
 
 static int LimiterWeno(mcfd_ctx *ctx, double w0, double eps, int phase, bool eigen) {
   if (int s = RequireMesh(ctx)) return s;
+  if (ctx->cfg.scheme == MCFD_DG_GENERAL) return Fail(ctx, MCFD_ERR_STATE, "the limiters are built for the nodal expansions");
   if (phase < -1 || phase > 1) return Fail(ctx, MCFD_ERR_ARG, "phase must be -1 (both), 0 (inner cells) or 1 (inter cells)");
   const int m = ctx->q == 3 ? 10 : 20, rows = ctx->q == 3 ? ModalShape<2>::kBasRows : ModalShape<3>::kBasRows;
   if (!ctx->bas.p) {   // first use: per-cell orthonormal bases, built on the host like the reference does at set-up

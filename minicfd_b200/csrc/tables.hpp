@@ -39,6 +39,17 @@ inline void LobattoRule(int q, double *x, double *w) {  // integrator/lobatto.hp
   }
 }
 
+inline void LegendreRule(int q, double *x, double *w) {  // integrator/legendre.hpp:50-73
+  if (q == 3) {
+    x[0] = -std::sqrt(0.6); x[1] = 0; x[2] = std::sqrt(0.6);
+    w[0] = 5.0 / 9.0; w[1] = 8.0 / 9.0; w[2] = 5.0 / 9.0;
+  } else {
+    const double a = std::sqrt((3 + 2 * std::sqrt(1.2)) / 7), b = std::sqrt((3 - 2 * std::sqrt(1.2)) / 7);
+    x[0] = -a; x[1] = -b; x[2] = b; x[3] = a;
+    w[0] = w[3] = (18 - std::sqrt(30.0)) / 36; w[1] = w[2] = (18 + std::sqrt(30.0)) / 36;
+  }
+}
+
 // l_m'(x_i): derivative of the m-th Lagrange polynomial at node i (basis/lagrange.hpp:72-133 obtains
 // the same numbers through a Taylor-matrix inverse).
 inline double LagrangeDerivative(int q, const double *x, int m, int i) {
@@ -130,6 +141,7 @@ inline Tables BuildTables(int degree, int scheme, int n_warps, int sub, double c
   double x[kMaxQ], w[kMaxQ];
   LobattoRule(q, x, w);
   for (int i = 0; i < q; ++i) { t.xi[i] = x[i]; t.w[i] = w[i]; }
+  LegendreRule(q, t.gx, t.gw);
   for (int i = 0; i < q; ++i)
     for (int m = 0; m < q; ++m) {
       t.d1[i][m] = LagrangeDerivative(q, x, m, i);
@@ -275,11 +287,12 @@ struct HostMesh {
   // Per-cell orthonormal basis of the modal extension (basis::OrthoNormal, basis/linear.hpp:87-141):
   // Gram-Schmidt on the Taylor monomials about the cell centre with the cell's own quadrature
   // (integrator/function.hpp:138-172).  Row layout per cell: ModalShape<P> in kernels.cuh.
-  std::vector<double> BuildModalBases(int degree) const {
+  std::vector<double> BuildModalBases(int degree, bool legendre = false) const {
     const int q = degree + 1, m = degree == 2 ? 10 : 20, tri = m * (m + 1) / 2, rows = 3 + tri + 3;
     const int64_t nc = n_local + n_ghost;
     double x[kMaxQ], w[kMaxQ];
-    LobattoRule(q, x, w);
+    if (legendre) LegendreRule(q, x, w);   // the stand-alone Projection of dg::General integrates with Gauss-Legendre
+    else LobattoRule(q, x, w);
     std::vector<double> bas((size_t)nc * rows, 0.0);
     std::vector<double> A(m * m), S(m * m);
     for (int64_t c = 0; c < nc; ++c) {
@@ -337,6 +350,44 @@ struct HostMesh {
       }
     }
     return bas;
+  }
+
+  // The same for dg::General: the Gauss-Legendre points of the boundary faces carrying `tag`, point (ia, ib) of a
+  // face at index ia*Q + ib with ia, ib running along the face's two local axes in increasing axis order (the order
+  // DgmStageCell reads its boundary values in; the reference evaluates the boundary function at
+  // face.integrator().GetGlobal(q), dg/general.hpp:131-133).
+  void BoundaryGaussPoints(Tables const &t, int degree, int tag, double *xyz) const {
+    const int q = degree + 1;
+    for (auto const &fr : bound_faces) {
+      if (fr.tag != tag) continue;
+      const int f = fr.holder_face;
+      const int d = (f == 2 || f == 4) ? 0 : (f == 1 || f == 3) ? 1 : 2;
+      const double sgn = (f == 2 || f == 3 || f == 5) ? 1.0 : -1.0;
+      const double *g = &coef[fr.holder * kGeomRows];
+      const double *o = &c0[fr.holder * 3];
+      for (int ia = 0; ia < q; ++ia) for (int ib = 0; ib < q; ++ib) {
+        const double a = t.gx[ia], b = t.gx[ib];
+        const double x = d == 0 ? sgn : a, e = d == 1 ? sgn : (d == 0 ? a : b), z = d == 2 ? sgn : b;
+        for (int k = 0; k < 3; ++k)
+          xyz[(ia * q + ib) * 3 + k] = o[k] + g[0 + k] * x + g[3 + k] * e + g[6 + k] * z + g[9 + k] * x * e
+              + g[12 + k] * e * z + g[15 + k] * z * x + g[18 + k] * x * e * z;
+      }
+      xyz += q * q * 3;
+    }
+  }
+  // Gauss-Legendre points of the local cells, [cell][Q^3][3] in the integrator's order (integrator/hexahedron.hpp:66-80)
+  void QuadraturePoints(Tables const &t, int degree, double *xyz) const {
+    const int q = degree + 1;
+    for (int64_t c = 0; c < n_local; ++c) {
+      const double *g = &coef[c * kGeomRows];
+      const double *o = &c0[c * 3];
+      for (int i = 0; i < q; ++i) for (int j = 0; j < q; ++j) for (int k2 = 0; k2 < q; ++k2) {
+        const double x = t.gx[i], e = t.gx[j], z = t.gx[k2];
+        for (int k = 0; k < 3; ++k)
+          *xyz++ = o[k] + g[0 + k] * x + g[3 + k] * e + g[6 + k] * z + g[9 + k] * x * e + g[12 + k] * e * z
+              + g[15 + k] * z * x + g[18 + k] * x * e * z;
+      }
+    }
   }
 
   bool Build(int degree, int64_t n_nodes, const double *xyz, int64_t nl, int64_t ng,

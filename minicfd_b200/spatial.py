@@ -18,6 +18,7 @@ class Spatial:
                  comm=None, fr_c_next=0.0, diffusion=capi.INVISCID):
         self.part = part
         self.degree = degree
+        self.scheme = scheme
         self.ctx = capi.Context(scheme, degree, riemann, device, fr_c_next, diffusion)
         self.kfields = self.ctx.kfields
         m = part.mesh
@@ -46,6 +47,11 @@ class Spatial:
 
     def Approximate(self, func):
         """fem.hpp:147-154: nodal sampling of func(xyz) on every local cell, then a halo exchange."""
+        if self.scheme == capi.DG_GENERAL:   # Projection::Approximate: L2 projection from the Gauss points
+            if self.comm is not None:
+                self.comm.drain()
+            self.ctx.project(np.asarray(func(self.ctx.quadrature_points())))
+            return
         pts = cell_points(self.part.mesh.nodes, self.part.cell_nodes[:self.part.n_local], self.degree)
         vals = np.asarray(func(pts))
         self.SetSolutionColumn(vals.reshape(-1))

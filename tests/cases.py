@@ -154,3 +154,7 @@ def cell_viscosities(n_cells, seed=1):
 ENERGY_GOLDEN_CASES = [("energy_p2_hllc", 2, 1), ("energy_p3_hllc", 3, 1)]
 ENERGY_BETAS = (2.0, 1.0 / 12)
 ENERGY_AMP = 5e-2          # noise level at which some, not all, (cell, component) pairs get a viscosity
+
+
+# ---- dg::General on the modal Projection polynomial with Gauss-Legendre rules ------------------
+DGM_GOLDEN_CASES = [("dgm_p2_hllc", 2, 1), ("dgm_p2_exact", 2, 0), ("dgm_p3_ausm", 3, 2)]

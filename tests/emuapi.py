@@ -118,6 +118,31 @@ def energy_viscosity(mesh, degree, betas, column=None, time_scale=1.0):
     return damping, (None if column is None else nu), (None if column is None else min_dt.value)
 
 
+def dgm(mesh, degree, riemann=1, column_in=None, *, tag_kinds=None, bvals=None, column_u0=None, mode=0, dt=0.0,
+        values=None, want_points=False):
+    """dg::General on the modal polynomial (single part): one stage / residual, or the L2 projection of `values`
+    given at the cells' Gauss points; want_points=True returns (boundary Gauss points, cell Gauss points) only."""
+    cells = np.ascontiguousarray(mesh.cells, dtype=np.int64)
+    bfaces = np.ascontiguousarray(mesh.bfaces, dtype=np.int64)
+    btags = np.ascontiguousarray(mesh.btags, dtype=np.int32)
+    nodes = np.ascontiguousarray(mesh.nodes, dtype=np.float64)
+    q = degree + 1
+    F = 5 * (10 if degree == 2 else 20)
+    kinds = np.zeros(16, dtype=np.int32)
+    for k, v in (tag_kinds or {}).items():
+        kinds[k] = v
+    gp = np.zeros((len(bfaces), q * q, 3)); qp = np.zeros((len(cells), q ** 3, 3))
+    out = None if want_points else np.empty(len(cells) * F)
+    arr = lambda a: None if a is None else np.ascontiguousarray(a, dtype=np.float64)
+    ci, cu, bv, vals = arr(column_in), arr(column_u0), arr(bvals), arr(values)
+    rc = lib().emu_dgm_stage(C.c_int(degree), C.c_int(riemann), C.c_int64(len(nodes)), _dp(nodes), C.c_int64(len(cells)),
+                             C.c_int64(0), _ip(cells), C.c_int64(len(bfaces)), _ip(bfaces), _i32(btags), _i32(kinds),
+                             _dp(bv), _dp(ci), _dp(cu), C.c_int(mode), C.c_double(dt), _dp(vals), _dp(out), _dp(gp), _dp(qp))
+    if rc != 0:
+        raise RuntimeError("emu_dgm_stage failed")
+    return (gp, qp) if want_points else out
+
+
 def riemann(kind, n, ul, ur, bc=-1):
     out = np.empty(5)
     n = np.ascontiguousarray(n, dtype=np.float64)

@@ -73,6 +73,20 @@ def main():
                             u_rk3=r.get_solution(), nu_rk3=r.cell_viscosity(),
                             nodes=m.nodes, cells=m.cells, bfaces=m.bfaces, btags=m.btags)
         print(name, int((nu > 0).sum()), "of", nu.size, "viscosities non-zero; dt", dt)
+    # dg::General<Part<Projection<Scalar, 3, P, 5>>, Riemann> with Legendre integrators
+    for name, degree, riemann in cases.DGM_GOLDEN_CASES:
+        r = refapi.Ref(m, degree=degree, scheme=refapi.DG_GENERAL, riemann=riemann)
+        cases.apply_bcs_ref(r)
+        r.approximate(refapi.F_SMOOTH, [1.0])
+        projected = r.get_solution()
+        u = projected * (1 + 1e-3 * np.random.default_rng(degree).uniform(-1, 1, projected.shape))
+        r.set_solution(u)
+        res = r.residual(cases.GOLDEN_T)
+        dt = r.time_step(1.0, 3)
+        r.rk_update(3, 0.0, cases.GOLDEN_DT, 1)
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), projected=projected, u=u, residual=res, dt=dt,
+                            u_rk3=r.get_solution(), nodes=m.nodes, cells=m.cells, bfaces=m.bfaces, btags=m.btags)
+        print(name, np.linalg.norm(res), dt)
     # WithLimiter<fr::Lobatto, weno::Lazy>: the limiter's action on a column, and an RK3 step with it
     for name, degree, riemann in cases.WENO_GOLDEN_CASES:
         r = refapi.Ref(m, degree=degree, scheme=refapi.FR_WENO_LAZY, riemann=riemann, weno=cases.WENO)

@@ -284,6 +284,70 @@ int emu_energy_viscosity(int degree, int64_t n_nodes, const double *xyz, int64_t
   return 0;
 }
 
+}  // extern "C"
+
+template <int Q>
+static void RunDgm(int riemann, DgmArgs a, const double *values, double *proj_out, int64_t nl, int64_t nc,
+    std::vector<double> &u, std::vector<double> &tay, const double *geom, const double *bas) {
+  if (values) {   // mcfd_project
+    for (int64_t c = 0; c < nl; ++c) DgmProjectCell<Q>(values, geom, bas, proj_out, (int)c);
+    return;
+  }
+  for (int64_t c = 0; c < nc; ++c) DgmTaylorCell<Q>(u.data(), bas, tay.data(), (int)(c >> 5), (int)(c & 31));
+  for (int64_t c = 0; c < nl; ++c) {
+    if (riemann == 0) DgmStageCell<Q, kExact>(a, (int)(c >> 5), (int)(c & 31));
+    else if (riemann == 1) DgmStageCell<Q, kHllc>(a, (int)(c >> 5), (int)(c & 31));
+    else DgmStageCell<Q, kAusm>(a, (int)(c >> 5), (int)(c & 31));
+  }
+}
+
+extern "C" {
+
+// dg::General on the modal polynomial, one stage on the host.  Columns hold 5 M coefficients per cell; with
+// `values` ([n_local][Q^3][5]) the call is the L2 projection instead and column_out receives the coefficients.
+// gauss_points_out (optional): [n_bfaces][Q*Q][3] boundary Gauss points in the library's boundary-face order.
+int emu_dgm_stage(int degree, int riemann, int64_t n_nodes, const double *xyz, int64_t n_local, int64_t n_ghost,
+    const int64_t *cell_nodes, int64_t n_bfaces, const int64_t *bface_nodes, const int32_t *bface_tags,
+    const int32_t *tag_kinds, const double *bvals, const double *column_in, const double *column_u0, int mode, double dt,
+    const double *values, double *column_out, double *gauss_points_out, double *quad_points_out) {
+  const int q = degree + 1, M = degree == 2 ? 10 : 20, F = 5 * M;
+  c_tab = BuildTables(degree, 0, (q == 3) ? kP2Warps : kP3Warps, kTile / ((q == 3) ? kP2Cells : kP3Cells));
+  HostMesh mesh;
+  if (!mesh.Build(degree, n_nodes, xyz, n_local, n_ghost, cell_nodes, n_bfaces, bface_nodes, bface_tags, 0, nullptr)) return -1;
+  const int64_t nc = n_local + n_ghost, nt = (nc + kTile - 1) / kTile;
+  if (gauss_points_out) {
+    int last = -1;
+    for (size_t b = 0; b < mesh.bound_faces.size(); ++b) {
+      const int tg = mesh.bound_faces[b].tag;
+      if (tg == last) continue;
+      last = tg;
+      mesh.BoundaryGaussPoints(c_tab, degree, tg, gauss_points_out + b * q * q * 3);
+    }
+  }
+  if (quad_points_out) mesh.QuadraturePoints(c_tab, degree, quad_points_out);
+  if (!column_out) return 0;
+  auto geom = ToTiles(mesh.coef, kGeomRows, nc, nt);
+  auto nbr = ToTiles(mesh.nbr, 6, nc, nt);
+  auto code = ToTiles(mesh.code, 6, nc, nt);
+  auto h2s = ToTiles(mesh.h2s, 18, nc, nt);
+  auto bas = ToTiles(mesh.BuildModalBases(degree, true), q == 3 ? ModalShape<2>::kBasRows : ModalShape<3>::kBasRows, nc, nt);
+  std::vector<unsigned char> bkind(mesh.bound_faces.size() + 1, 0);
+  for (size_t b = 0; b < mesh.bound_faces.size(); ++b) bkind[b] = (unsigned char)tag_kinds[mesh.bound_faces[b].tag];
+  std::vector<double> zero_vals((mesh.bound_faces.size() + 1) * q * q * 5, 0.0);
+  std::vector<double> u((size_t)nt * F * kTile, 0.0), u0(u.size(), 0.0), out(u.size(), 0.0), tay(u.size(), 0.0);
+  if (column_in) for (int64_t c = 0; c < nc; ++c) for (int f = 0; f < F; ++f) u[((c >> 5) * F + f) * kTile + (c & 31)] = column_in[c * F + f];
+  if (column_u0) for (int64_t c = 0; c < n_local; ++c) for (int f = 0; f < F; ++f) u0[((c >> 5) * F + f) * kTile + (c & 31)] = column_u0[c * F + f];
+  else u0 = u;
+  DgmArgs a;
+  a.u_in = u.data(); a.u0 = u0.data(); a.u_out = out.data(); a.tay = tay.data(); a.geom = geom.data(); a.bas = bas.data();
+  a.h2s = h2s.data(); a.nbr = nbr.data(); a.code = code.data(); a.bkind = bkind.data();
+  a.bvals = bvals ? bvals : zero_vals.data(); a.cell_begin = 0; a.cell_end = (int)n_local; a.mode = mode; a.dt = dt; a.dt_dev = nullptr;
+  if (q == 3) RunDgm<3>(riemann, a, values, out.data(), n_local, nc, u, tay, geom.data(), bas.data());
+  else RunDgm<4>(riemann, a, values, out.data(), n_local, nc, u, tay, geom.data(), bas.data());
+  for (int64_t c = 0; c < n_local; ++c) for (int f = 0; f < F; ++f) column_out[c * F + f] = out[((c >> 5) * F + f) * kTile + (c & 31)];
+  return 0;
+}
+
 // Boundary-face order and flux-point coordinates as the library defines them.
 int64_t emu_boundary(int degree, int64_t n_nodes, const double *xyz, int64_t n_local, int64_t n_ghost,
     const int64_t *cell_nodes, int64_t n_bfaces, const int64_t *bface_nodes, const int32_t *bface_tags,

@@ -169,6 +169,28 @@ def test_energy_viscosity_kernel_source_on_host_matches_golden(name, degree, rie
     assert min(1.0, cfl * min_dt) == pytest.approx(float(g["dt"]), rel=1e-13)
 
 
+@pytest.mark.parametrize("name,degree,riemann", cases.DGM_GOLDEN_CASES)
+def test_dg_general_kernel_source_on_host_matches_golden(name, degree, riemann):
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    m = meshmod.HexMesh(nodes=g["nodes"], cells=g["cells"], bfaces=g["bfaces"], btags=g["btags"])
+    gp, qp = emuapi.dgm(m, degree, want_points=True)
+    assert relerr(emuapi.dgm(m, degree, riemann, values=fields.smooth(1.0)(qp, 0.0)), g["projected"]) < 1e-12
+    holder, hf, tags, _ = emuapi.boundary(m, degree)
+    def bvals(t):
+        out = np.zeros(gp.shape[:2] + (5,))
+        for tag, kind in cases.MIXED_BCS.items():
+            sel = tags == tag
+            out[sel] = cases.bc_function(kind)(gp[sel], t)
+        return out
+    kw = dict(tag_kinds=cases.MIXED_BCS)
+    assert relerr(emuapi.dgm(m, degree, riemann, g["u"], bvals=bvals(cases.GOLDEN_T), **kw), g["residual"]) < 1e-12
+    dt = cases.GOLDEN_DT
+    u1 = emuapi.dgm(m, degree, riemann, g["u"], bvals=bvals(0.0), mode=1, dt=dt, **kw)
+    u2 = emuapi.dgm(m, degree, riemann, u1, bvals=bvals(dt), column_u0=g["u"], mode=2, dt=dt, **kw)
+    u3 = emuapi.dgm(m, degree, riemann, u2, bvals=bvals(dt / 2), column_u0=g["u"], mode=3, dt=dt, **kw)
+    assert relerr(u3, g["u_rk3"]) < 1e-12
+
+
 @pytest.mark.parametrize("name,degree,riemann", cases.WENO_EIGEN_GOLDEN_CASES)
 def test_weno_eigen_kernel_source_on_host_matches_golden(name, degree, riemann):
     g = np.load(os.path.join(GOLDEN, name + ".npz"))

@@ -210,6 +210,18 @@ def test_c_oracle_fr_general_navier_stokes_matches_reference(degree, riemann, c_
     assert relerr(o.rk_update(u, 3, 0.0, 1e-3), r.get_solution()) < TOL
 
 
+@pytest.mark.parametrize("name,degree,riemann", cases.DGM_GOLDEN_CASES)
+def test_c_oracle_dg_general_matches_golden(name, degree, riemann):
+    """dg::General on the modal Projection polynomial (SURVEY row a7): projection, residual, time step, RK3."""
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    o = oc.Oracle(_golden_mesh(g), degree, 9, riemann)
+    cases.apply_bcs_oracle(o)
+    assert relerr(o.approximate(oc.F_SMOOTH, [1.0]), g["projected"]) < TOL
+    assert relerr(o.residual(g["u"], cases.GOLDEN_T), g["residual"]) < TOL
+    assert o.time_step(g["u"], 1.0, 3) == pytest.approx(float(g["dt"]), rel=1e-14)
+    assert relerr(o.rk_update(g["u"], 3, 0.0, cases.GOLDEN_DT), g["u_rk3"]) < TOL
+
+
 def _flux_1d(rho, u, p):
     """Flux of a 1-D primitive state (test/riemann/euler/exact.cpp:34-39)."""
     e = p / 0.4 + 0.5 * rho * u * u
