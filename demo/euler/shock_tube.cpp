@@ -28,11 +28,19 @@ using Riemann = mini::riemann::rotated::Euler<Unrotated>;
 
 constexpr int kComponents = 5;
 constexpr int kDegrees = 2;
+#ifdef DGFEM   // demo/euler/sourceless.hpp:28-33
+#include "mini/integrator/legendre.hpp"
+using Gx = mini::integrator::Legendre<Scalar, kDegrees + 1>;
+#include "mini/polynomial/projection.hpp"
+using Polynomial = mini::polynomial::Projection<Scalar, kDimensions, kDegrees, kComponents>;
+#else
 #include "mini/integrator/lobatto.hpp"
 using Gx = mini::integrator::Lobatto<Scalar, kDegrees + 1>;
 #include "mini/polynomial/hexahedron.hpp"
 using Interpolation = mini::polynomial::Hexahedron<Gx, Gx, Gx, kComponents, false>;
-#ifdef LIMITER   // demo/euler/sourceless.hpp:41-47
+#endif
+#ifdef DGFEM
+#elif defined(LIMITER)   // demo/euler/sourceless.hpp:41-47
 #include "mini/polynomial/extrapolation.hpp"
 using Polynomial = mini::polynomial::Extrapolation<Interpolation>;
 #else
@@ -44,7 +52,10 @@ using Cell = typename Part::Cell;
 using Global = typename Part::Global;
 using Value = typename Part::Value;
 #include "mini/spatial/fr/lobatto.hpp"
-#ifdef LIMITER   // demo/euler/sourceless.hpp:60-80
+#ifdef DGFEM     // demo/euler/sourceless.hpp:64-66 (without the limiter)
+#include "mini/spatial/dg/general.hpp"
+using Spatial = mini::spatial::dg::General<Part, Riemann>;
+#elif defined(LIMITER)   // demo/euler/sourceless.hpp:60-80
 using General = mini::spatial::fr::Lobatto<Part, Riemann>;
 #include "mini/limiter/weno.hpp"
 #include "mini/limiter/reconstruct.hpp"

@@ -66,6 +66,11 @@ struct Lobatto {  // integrator/lobatto.hpp:20-93
     else return {-1.0, -std::sqrt(1.0 / 5), std::sqrt(1.0 / 5), 1.0};
   }
 };
+template <typename S, int N>
+struct Legendre {  // integrator/legendre.hpp:20-80; the rule itself lives in the library (MCFD_DG_GENERAL)
+  using Scalar = S;
+  static constexpr int Q = N;
+};
 }  // namespace integrator
 
 namespace polynomial {
@@ -80,6 +85,24 @@ struct Hexahedron {  // polynomial/hexahedron.hpp:41-65
   static constexpr bool kLocal = kL;
   static constexpr int P = Gx::Q - 1;
   static constexpr int N = Gx::Q * Gx::Q * Gx::Q;
+  static constexpr int K = kComponents;
+  static constexpr int D = 3;
+  static constexpr int kFields = K * N;
+  using Global = algebra::Vector<Scalar, 3>;
+  using Local = Global;
+  using Value = algebra::Vector<Scalar, K>;
+};
+// polynomial/projection.hpp:67-176: the stand-alone modal expansion on the cell's orthonormal basis, K x M coefficients
+// per cell (M = 10 at P = 2, 20 at P = 3).  A tag here: the basis and the quadrature live in the library.
+template <typename S, int kDimensions, int kDegrees, int kComponents>
+struct Projection {
+  static_assert(kDimensions == 3 && (kDegrees == 2 || kDegrees == 3), "three-dimensional, degree 2 or 3");
+  using Scalar = S;
+  static constexpr bool kLocal = false;
+  static constexpr bool kModalOnly = true;
+  static constexpr int P = kDegrees;
+  static constexpr int Q = kDegrees + 1;                                  // Gauss-Legendre points per direction
+  static constexpr int N = (kDegrees + 1) * (kDegrees + 2) * (kDegrees + 3) / 6;   // basis/taylor.hpp:27-31
   static constexpr int K = kComponents;
   static constexpr int D = 3;
   static constexpr int kFields = K * N;
@@ -411,15 +434,29 @@ class FiniteElementB200 : public temporal::System<typename P::Scalar> {
 
   template <class Callable>
   void Approximate(Callable &&func) {  // fem.hpp:147-154
-    Column column(part().GetCellDataSize());
-    constexpr int N = Part::Polynomial::N, K = Part::kComponents;
-    for (typename Part::Index c = 0; c < part().CountLocalCells(); ++c) {
-      for (int q = 0; q < N; ++q) {
-        Value v = func(part().NodeCoordinate(c, q));
-        for (int k = 0; k < K; ++k) column[(c * N + q) * K + k] = v[k];
+    if constexpr (requires { Part::Polynomial::kModalOnly; }) {   // Projection::Approximate: L2 projection
+      constexpr int Q = Part::Polynomial::Q, n_points = Q * Q * Q, K = Part::kComponents;
+      const size_t n_cells = (size_t)part().CountLocalCells();
+      std::vector<double> xyz(n_cells * n_points * 3), values(n_cells * n_points * K);
+      b200::Check(mcfd_get_quadrature_points(ctx_, xyz.data()), ctx_, "mcfd_get_quadrature_points");
+      for (size_t i = 0; i < n_cells * n_points; ++i) {
+        Global x;
+        for (int d = 0; d < 3; ++d) x[d] = xyz[i * 3 + d];
+        Value v = func(x);
+        for (int k = 0; k < K; ++k) values[i * K + k] = v[k];
       }
+      b200::Check(mcfd_project(ctx_, values.data()), ctx_, "mcfd_project");
+    } else {
+      Column column(part().GetCellDataSize());
+      constexpr int N = Part::Polynomial::N, K = Part::kComponents;
+      for (typename Part::Index c = 0; c < part().CountLocalCells(); ++c) {
+        for (int q = 0; q < N; ++q) {
+          Value v = func(part().NodeCoordinate(c, q));
+          for (int k = 0; k < K; ++k) column[(c * N + q) * K + k] = v[k];
+        }
+      }
+      SetSolutionColumn(column);
     }
-    SetSolutionColumn(column);
   }
 
   // fem.hpp:196-222
@@ -600,6 +637,13 @@ class General : public FiniteElementB200<P, R, MCFD_FR_GENERAL> {  // spatial/fr
 };
 }  // namespace fr
 namespace dg {
+template <typename P, typename R>
+class General : public FiniteElementB200<P, R, MCFD_DG_GENERAL> {  // spatial/dg/general.hpp:20-200
+ public:
+  static_assert(P::Polynomial::kModalOnly, "dg::General is built for the modal Projection polynomial");
+  using FiniteElementB200<P, R, MCFD_DG_GENERAL>::FiniteElementB200;
+  std::string name() const { return "DG::General"; }
+};
 template <typename P, typename R>
 class Lobatto : public FiniteElementB200<P, R, MCFD_DG_LOBATTO> {  // spatial/dg/lobatto.hpp:32-303
  public:

@@ -102,6 +102,50 @@ def test_sod_driver_with_weno_limiter_through_cpp_template_api(tmp_path, eigen):
     assert np.abs(got - ref).max() / np.abs(ref).max() < 1e-11
 
 
+def _sod_dgfem_reference(n_steps):
+    """Sod with dg::General on the modal polynomial (the reference's DGFEM build), HLLC."""
+    m = meshmod.box(50, 2, 3, hi=(5.0, 0.2, 0.3))
+    left = np.array([1.0, 0, 0, 0, 1.0 / 0.4]); right = np.array([0.125, 0, 0, 0, 0.1 / 0.4])
+    dt_max = 0.2 / 200
+    if refapi.available(2):
+        r = refapi.Ref(m, degree=2, scheme=refapi.DG_GENERAL, riemann=1)
+        def ic(tag, xyz, t, out, user):
+            v = left if xyz[0] < 2.5 else right
+            for k in range(5):
+                out[k] = v[k]
+        r.approximate(refapi.F_CALLBACK, cb=ic)
+        r.set_bc(meshmod.XMIN, refapi.SMART, refapi.F_CONST, left)
+        r.set_bc(meshmod.XMAX, refapi.SMART, refapi.F_CONST, right)
+        for tag in (meshmod.YMIN, meshmod.YMAX, meshmod.ZMIN, meshmod.ZMAX):
+            r.set_bc(tag, refapi.WALL)
+        t = 0.0
+        for _ in range(n_steps):
+            dt = r.time_step(dt_max, 3)
+            r.rk_update(3, t, dt, 1)
+            t += dt
+        return r.get_solution()
+    return None
+
+
+def test_sod_driver_dgfem_through_cpp_template_api(tmp_path):
+    """-DDGFEM: Legendre rules, the modal Projection polynomial and dg::General as demo/euler/sourceless.hpp:28-33,
+    64-66 name them; Approximate is the L2 projection at the Gauss points."""
+    ref = _sod_dgfem_reference(10)
+    if ref is None:
+        pytest.skip("oracle/_ref not shipped")
+    exe = tmp_path / "shock_tube_dgfem"
+    subprocess.check_call(["g++", "-DUSE_HLLC", "-DDGFEM", "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "demo", "euler", "shock_tube.cpp"), "-o", str(exe),
+                           "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200",
+                           "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")])
+    out = tmp_path / "column.bin"
+    res = subprocess.run([str(exe), "10", str(out)], capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout + res.stderr
+    got = np.fromfile(out, dtype=np.float64)
+    assert got.shape == ref.shape == (300 * 50,)
+    assert np.abs(got - ref).max() / np.abs(ref).max() < 1e-12
+
+
 def _cavity_reference(n, n_steps):
     """demo/laminar/cavity.cpp's loop on the CPU checker (Navier-Stokes + direct DG, no-slip walls)."""
     m = meshmod.box(n, n, 2, hi=(1.0, 1.0, 0.25))
