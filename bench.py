@@ -34,6 +34,7 @@ sys.path.insert(0, ROOT)
 import numpy as np  # noqa: E402
 
 B_ALG_P2 = 24.0 + 192.0 / 135.0   # algorithmic bytes per DOF-update
+SCHEME_NAME = {"fr": "FR-Lobatto", "dg": "DG-Lobatto", "dgm": "dg::General (modal Projection, Gauss-Legendre)"}
 RIEMANN = {"exact": 0, "hllc": 1, "ausm": 2}
 
 
@@ -46,7 +47,8 @@ def parse():
     ap.add_argument("--cells", type=int, default=42, help="cells per direction per GPU")
     ap.add_argument("--degree", type=int, default=2)
     ap.add_argument("--riemann", default="hllc", choices=list(RIEMANN))
-    ap.add_argument("--scheme", default="fr", choices=["fr", "dg"])
+    ap.add_argument("--scheme", default="fr", choices=["fr", "dg", "dgm"],
+                    help="fr: FR-Lobatto (headline), dg: DGSEM-Lobatto, dgm: dg::General on the modal Projection polynomial")
     ap.add_argument("--cpu-cells", type=int, default=0, help="cells per direction of the CPU sample (0 = auto)")
     ap.add_argument("--viscous", type=float, default=None, metavar="NU",
                     help="run the Navier-Stokes + direct-DG path with this kinematic viscosity (not the headline workload)")
@@ -136,7 +138,7 @@ def cpu_run(args, steps, warmup, cells=None):
     from minicfd_b200 import mesh as meshmod
     from minicfd_b200.part import cell_points
     cores = os.cpu_count() or 1
-    scheme = 0 if args.scheme == "fr" else 1
+    scheme = {"fr": 0, "dg": 1, "dgm": 9}[args.scheme]
     if args.viscous is not None:
         scheme = 3
     if args.limiter:
@@ -145,6 +147,8 @@ def cpu_run(args, steps, warmup, cells=None):
         scheme = 7
     riemann = RIEMANN[args.riemann]
     kf = 5 * (args.degree + 1) ** 3
+    if args.scheme == "dgm":
+        kf = 5 * (10 if args.degree == 2 else 20)
     if refapi.available(args.degree):
         kind = "reference"
         n_parts = max(1, min(cores, 64))
@@ -192,7 +196,7 @@ def cpu_run(args, steps, warmup, cells=None):
     dt_wall = time.perf_counter() - t0
     n_dof = m.n_cells * kf
     value = 3.0 * n_dof * steps / dt_wall
-    sample = (f"{n}^3 Hexahedron8 cells ({n_dof} DOF), {args.scheme.upper()}-Lobatto p={args.degree}, "
+    sample = (f"{n}^3 Hexahedron8 cells ({n_dof} DOF), {SCHEME_NAME[args.scheme]} p={args.degree}, "
               f"{args.riemann}, RK3 incl. GetTimeStep, inviscid walls, {n_parts} part(s)/thread(s), "
               f"{steps} step(s) after {warmup} warm-up")
     return {"value": value, "unit": "DOF-updates/s", "cores": n_parts, "kind": kind, "sample": sample,
@@ -207,7 +211,7 @@ def config_dict(args, n_gpus, dims, part):
                         ("weno::Lazy limiter after every stage, " if args.limiter else "") +
                         ("EnergyBasedViscosity updated after every stage, " if args.energy_viscosity else "") +
                         
-                        f"{args.scheme.upper()}-Lobatto p={args.degree}, {args.riemann.upper()}, RK3, periodic",
+                        f"{SCHEME_NAME[args.scheme]} p={args.degree}, {args.riemann.upper()}, RK3, periodic",
             "cells_per_gpu": args.cells ** 3, "dof_per_gpu": args.cells ** 3 * 5 * (args.degree + 1) ** 3,
             "step": "GetTimeStep + RungeKutta<3>::Update (3 stages)", "parallelism": f"domain decomposition {part}",
             "l2_policy": "state (3 x 80 MB per GPU) exceeds the 126 MB L2; no flush needed"}
@@ -261,8 +265,9 @@ def ours(args):
     m = meshmod.box(*dims, hi=(10.0 * px, 10.0 * py, 10.0 * pz), periodic=True)
     parts = meshmod.block_partition(m, px, py, pz) if world > 1 else None
     part = Part(m, parts, rank, world)
-    scheme = capi.FR_LOBATTO if args.scheme == "fr" else capi.DG_LOBATTO
-    comm = halo.for_part(part, 5 * (args.degree + 1) ** 3) if world > 1 else None
+    scheme = {"fr": capi.FR_LOBATTO, "dg": capi.DG_LOBATTO, "dgm": capi.DG_GENERAL}[args.scheme]
+    kf_halo = 5 * (args.degree + 1) ** 3 if args.scheme != "dgm" else 5 * (10 if args.degree == 2 else 20)
+    comm = halo.for_part(part, kf_halo) if world > 1 else None
     sp = Spatial(part, scheme=scheme, degree=args.degree, riemann=RIEMANN[args.riemann], device=local_rank,
                  comm=comm, diffusion=capi.CELL_VISCOSITY_DDG if args.energy_viscosity else
                  (capi.INVISCID if args.viscous is None else capi.NAVIER_STOKES_DDG))

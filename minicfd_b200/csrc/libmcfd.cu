@@ -225,20 +225,6 @@ cudaError_t LaunchDgmQ(mcfd_ctx *ctx, DgmArgs const &a, int t0, int n_tiles) {
 int LaunchStage(mcfd_ctx *ctx, const double *u_in, const double *u0, double *u_out, int mode,
     double dt, int64_t block_begin, int64_t block_end) {
   if (block_end <= block_begin) return MCFD_OK;
-  if (ctx->cfg.scheme == MCFD_DG_GENERAL) {   // blocks are tiles here
-    DgmArgs d;
-    d.u_in = u_in; d.u0 = u0; d.u_out = u_out; d.tay = ctx->tay.p; d.geom = ctx->geom.p; d.bas = ctx->bas.p;
-    d.h2s = ctx->h2s.p; d.nbr = ctx->nbr.p; d.code = ctx->code.p; d.bkind = ctx->bkind.p; d.bvals = ctx->bvals.p;
-    d.cell_begin = (int)(block_begin * kTile);
-    d.cell_end = (int)std::min<int64_t>(block_end * kTile, ctx->mesh.n_local);
-    d.mode = mode; d.dt = dt; d.dt_dev = ctx->rk_order ? ctx->rk_dt_dev : nullptr;
-    MCFD_CUDA(ctx, EnsureTables(ctx));
-    cudaError_t e = ctx->q == 3 ? LaunchDgmQ<3>(ctx, d, (int)block_begin, (int)(block_end - block_begin))
-                                : LaunchDgmQ<4>(ctx, d, (int)block_begin, (int)(block_end - block_begin));
-    if (e != cudaSuccess) return Fail(ctx, MCFD_ERR_CUDA, std::string("dg::General stage kernel: ") + cudaGetErrorString(e));
-    ctx->launches++;
-    return MCFD_OK;
-  }
   StageArgs a;
   a.u_in = u_in; a.u0 = u0; a.u_out = u_out;
   a.geom = ctx->geom.p; a.nbr = ctx->nbr.p; a.code = ctx->code.p;
@@ -263,7 +249,17 @@ int LaunchStage(mcfd_ctx *ctx, const double *u_in, const double *u0, double *u_o
     MCFD_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
   }
   cudaError_t e;
-  if (ctx->cfg.diffusion != MCFD_INVISCID) {
+  if (ctx->cfg.scheme == MCFD_DG_GENERAL) {   // blocks are tiles here
+    DgmArgs d;
+    d.u_in = u_in; d.u0 = u0; d.u_out = u_out; d.tay = ctx->tay.p; d.geom = ctx->geom.p; d.bas = ctx->bas.p;
+    d.h2s = ctx->h2s.p; d.nbr = ctx->nbr.p; d.code = ctx->code.p; d.bkind = ctx->bkind.p; d.bvals = ctx->bvals.p;
+    d.cell_begin = (int)(block_begin * kTile);
+    d.cell_end = (int)std::min<int64_t>(block_end * kTile, ctx->mesh.n_local);
+    d.mode = mode; d.dt = dt; d.dt_dev = ctx->rk_order ? ctx->rk_dt_dev : nullptr;
+    MCFD_CUDA(ctx, EnsureTables(ctx));
+    e = ctx->q == 3 ? LaunchDgmQ<3>(ctx, d, (int)block_begin, (int)(block_end - block_begin))
+                                : LaunchDgmQ<4>(ctx, d, (int)block_begin, (int)(block_end - block_begin));
+  } else if (ctx->cfg.diffusion != MCFD_INVISCID) {
     e = (ctx->q == 3) ? LaunchStageViscous<3, kP2Cells, kP2ViscousWarps>(ctx, a, n_blocks)
                       : LaunchStageViscous<4, kP3Cells, kP3Warps>(ctx, a, n_blocks);
   } else {
