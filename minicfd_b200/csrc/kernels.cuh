@@ -914,17 +914,18 @@ MCFD_HD void TaylorDerivativeSquares(const double *d, const double *c, double *s
 
 // offset of quadrature point n from the cell centre, and its global weight (local weight x det J)
 template <int Q>
-MCFD_HD void QuadraturePoint(int n, const double *geo, int gs, double *d, double *w) {
+MCFD_HD void QuadraturePoint(int n, const double *geo, int gs, double *d, double *w, bool legendre = false) {
   constexpr int FQ = Q * Q;
   const int i = n / FQ, j = (n / Q) % Q, k = n % Q;
-  const double x = c_tab.xi[i], e = c_tab.xi[j], z = c_tab.xi[k];
+  const double *px = legendre ? c_tab.gx : c_tab.xi, *pw = legendre ? c_tab.gw : c_tab.w;
+  const double x = px[i], e = px[j], z = px[k];
 #pragma unroll
   for (int a = 0; a < 3; ++a) {
     d[a] = geo[(0 + a) * gs] * x + geo[(3 + a) * gs] * e + geo[(6 + a) * gs] * z + geo[(9 + a) * gs] * (x * e)
          + geo[(12 + a) * gs] * (e * z) + geo[(15 + a) * gs] * (z * x) + geo[(18 + a) * gs] * (x * e * z);
   }
   const Metric m = ComputeMetric(geo, gs, x, e, z);
-  *w = c_tab.w[i] * c_tab.w[j] * c_tab.w[k] * m.det;
+  *w = pw[i] * pw[j] * pw[k] * m.det;
 }
 
 // a = S g (orthonormal coefficients from Taylor moments) and t = S^T a (Taylor coefficients);
@@ -997,6 +998,10 @@ struct WenoArgs {
   double *mod_new, *tay_new;  // the limited cells' new coefficients (copied over after the batch)
   int cell_begin, cell_end;
   double w0, eps;
+  // coefficient (comp, k) of a cell sits at row comp*comp_stride + k*mode_stride of its 5 M rows: (M, 1) for the
+  // limiter's own tables, (1, 5) when the tables ARE a modal state (dg::General on Projection cells: modal_state != 0,
+  // the blend is written straight into `u`, nothing is resampled, the rule is Gauss-Legendre)
+  int comp_stride, mode_stride, modal_state, legendre;
 };
 
 // weno::Lazy::Reconstruct for one (cell, component) (limiter/weno.hpp:127-194) + Extrapolation::SetCoeff
@@ -1008,8 +1013,9 @@ MCFD_HD void WenoLazyCell(const WenoArgs &p, int tile, int tl, int comp, const d
   const double *S = bas + (size_t)ModalShape<P>::kSOffset * bs;
   const double s00 = S[0];
   double mine[M], fresh[M];
-  const double *my_mod = p.mod + ((size_t)tile * 5 * M + comp * M) * kTile + tl;
-  for (int k = 0; k < M; ++k) { mine[k] = my_mod[(size_t)k * kTile]; fresh[k] = 0; }
+  const size_t ms = (size_t)p.mode_stride * kTile;
+  const double *my_mod = p.mod + ((size_t)tile * 5 * M + comp * p.comp_stride) * kTile + tl;
+  for (int k = 0; k < M; ++k) { mine[k] = my_mod[k * ms]; fresh[k] = 0; }
   const double my_average = mine[0] * s00;                  // projection.hpp:46-51
   int adj_cnt = 0;
   double sum_w = 0;
@@ -1022,9 +1028,9 @@ MCFD_HD void WenoLazyCell(const WenoArgs &p, int tile, int tl, int comp, const d
     const double *hv = p.h2s + ((size_t)tile * 18 + f * 3) * kTile + tl;
     const double sg = holder ? 1.0 : -1.0;
     const double off[3] = {sg * hv[0], sg * hv[kTile], sg * hv[2 * kTile]};
-    const double *nt = p.tay + ((size_t)(nb >> 5) * 5 * M + comp * M) * kTile + (nb & 31);
+    const double *nt = p.tay + ((size_t)(nb >> 5) * 5 * M + comp * p.comp_stride) * kTile + (nb & 31);
     double tb[M], g[M], cand[M];
-    for (int k = 0; k < M; ++k) { tb[k] = nt[(size_t)k * kTile]; g[k] = 0; }
+    for (int k = 0; k < M; ++k) { tb[k] = nt[k * ms]; g[k] = 0; }
     for (int n = 0; n < N; ++n) {   // Borrow: neighbour's polynomial at my quadrature points, projected on my basis
       const double d[3] = {quad[(size_t)(n * 4) * qs], quad[(size_t)(n * 4 + 1) * qs], quad[(size_t)(n * 4 + 2) * qs]};
       const double dn[3] = {d[0] - off[0], d[1] - off[1], d[2] - off[2]};
@@ -1051,6 +1057,11 @@ MCFD_HD void WenoLazyCell(const WenoArgs &p, int tile, int tl, int comp, const d
   }
   const double inv = 1.0 / sum_w;
   for (int k = 0; k < M; ++k) fresh[k] *= inv;
+  if (p.modal_state) {   // Projection::SetCoeff: the blend is the new state
+    double *state = p.u + ((size_t)tile * 5 * M + comp * p.comp_stride) * kTile + tl;
+    for (int k = 0; k < M; ++k) state[k * ms] = fresh[k];
+    return;
+  }
   double t[M];
   ModalToTaylor<M>(S, bs, fresh, t);
   double *new_mod = p.mod_new + ((size_t)tile * 5 * M + comp * M) * kTile + tl;
@@ -1266,12 +1277,13 @@ struct WenoShape {
   static constexpr size_t kSharedBytes = (size_t)(N * 4 + ModalShape<P>::kBasRows) * kTile * sizeof(double);
 };
 template <int Q>
-__device__ __forceinline__ void WenoStage(const double *geom, const double *bas, int tile, double *sQuad, double *sBas) {
+__device__ __forceinline__ void WenoStage(const double *geom, const double *bas, int tile, double *sQuad, double *sBas,
+    bool legendre = false) {
   constexpr int N = Q * Q * Q, kBasRows = ModalShape<Q - 1>::kBasRows;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int n = warp; n < N; n += 5) {
     double d[3], w;
-    QuadraturePoint<Q>(n, geom + (size_t)tile * kGeomRows * kTile + lane, kTile, d, &w);
+    QuadraturePoint<Q>(n, geom + (size_t)tile * kGeomRows * kTile + lane, kTile, d, &w, legendre);
     sQuad[(n * 4 + 0) * kTile + lane] = d[0]; sQuad[(n * 4 + 1) * kTile + lane] = d[1];
     sQuad[(n * 4 + 2) * kTile + lane] = d[2]; sQuad[(n * 4 + 3) * kTile + lane] = w;
   }
@@ -1297,7 +1309,7 @@ __global__ void __launch_bounds__(160) WenoLazyKernel(WenoArgs p, int tile_begin
   extern __shared__ double smem[];
   double *sQuad = smem, *sBas = smem + N * 4 * kTile;
   const int tile = tile_begin + blockIdx.x, lane = threadIdx.x & 31, comp = threadIdx.x >> 5;
-  WenoStage<Q>(p.geom, p.bas, tile, sQuad, sBas);
+  WenoStage<Q>(p.geom, p.bas, tile, sQuad, sBas, p.legendre != 0);
   const int cell = tile * kTile + lane;
   if (cell < p.cell_begin || cell >= p.cell_end) return;
   WenoLazyCell<Q>(p, tile, lane, comp, sQuad + lane, kTile, sBas + lane, kTile);

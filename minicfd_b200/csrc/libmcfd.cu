@@ -1003,6 +1003,7 @@ int WenoLazyBatch(mcfd_ctx *ctx, double *u, double w0, double eps, int64_t modal
     a.u = u; a.geom = ctx->geom.p; a.bas = ctx->bas.p; a.h2s = ctx->h2s.p; a.nbr = ctx->nbr.p; a.code = ctx->code.p;
     a.mod = ctx->mod.p; a.tay = ctx->tay.p; a.mod_new = ctx->mod_new.p; a.tay_new = ctx->tay_new.p;
     a.cell_begin = (int)cell_begin; a.cell_end = (int)cell_end; a.w0 = w0; a.eps = eps;
+    a.comp_stride = M; a.mode_stride = 1; a.modal_state = 0; a.legendre = 0;
     const int t0 = (int)(cell_begin / kTile), t1 = (int)((cell_end + kTile - 1) / kTile);
     if (eigen) {
       WenoEigenArgs e;
@@ -1021,6 +1022,33 @@ int WenoLazyBatch(mcfd_ctx *ctx, double *u, double w0, double eps, int64_t modal
     }
   }
   MCFD_CUDA(ctx, cudaGetLastError());
+  return MCFD_OK;
+}
+
+// weno::Lazy on Projection cells (dg::General): the modal state is limited in place; its Taylor form is all the
+// neighbours read, so a batch is: Taylor form of the cells whose coefficients are new -> blend
+template <int Q>
+int DgmWenoBatch(mcfd_ctx *ctx, double *u, double w0, double eps, int64_t taylor_begin, int64_t taylor_end,
+    int64_t cell_begin, int64_t cell_end) {
+  constexpr int M = ModalShape<Q - 1>::M;
+  const size_t smem = WenoShape<Q>::kSharedBytes;
+  static bool configured = false;
+  if (!configured) {
+    MCFD_CUDA(ctx, cudaFuncSetAttribute(WenoLazyKernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = true;
+  }
+  if (int s = LaunchDgmTaylor(ctx, u, taylor_begin, taylor_end)) return s;
+  if (cell_end <= cell_begin) return MCFD_OK;
+  WenoArgs a;
+  a.u = u; a.geom = ctx->geom.p; a.bas = ctx->bas.p; a.h2s = ctx->h2s.p; a.nbr = ctx->nbr.p; a.code = ctx->code.p;
+  a.mod = u; a.tay = ctx->tay.p; a.mod_new = nullptr; a.tay_new = nullptr;
+  a.cell_begin = (int)cell_begin; a.cell_end = (int)cell_end; a.w0 = w0; a.eps = eps;
+  a.comp_stride = 1; a.mode_stride = 5; a.modal_state = 1; a.legendre = 1;
+  (void)M;
+  const int t0 = (int)(cell_begin / kTile), t1 = (int)((cell_end + kTile - 1) / kTile);
+  WenoLazyKernel<Q><<<t1 - t0, 160, smem, ctx->stream>>>(a, t0);
+  MCFD_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
   return MCFD_OK;
 }
 
@@ -1059,7 +1087,23 @@ int mcfd_eigen_matrices(mcfd_ctx *ctx, int64_t n, const double *conservative, co
 
 static int LimiterWeno(mcfd_ctx *ctx, double w0, double eps, int phase, bool eigen) {
   if (int s = RequireMesh(ctx)) return s;
-  if (ctx->cfg.scheme == MCFD_DG_GENERAL) return Fail(ctx, MCFD_ERR_STATE, "the limiters are built for the nodal expansions");
+  if (ctx->cfg.scheme == MCFD_DG_GENERAL) {
+    if (eigen) return Fail(ctx, MCFD_ERR_STATE, "weno::Eigen is built for the nodal expansions");
+    if (phase < -1 || phase > 1) return Fail(ctx, MCFD_ERR_ARG, "phase must be -1 (both), 0 (inner cells) or 1 (inter cells)");
+    double *u = HaloState(ctx);
+    const int64_t nl = ctx->mesh.n_local, nc = ctx->n_cells, fi = ctx->mesh.n_ghost ? ctx->first_inter : nl;
+    auto batch = [&](int64_t tb, int64_t te, int64_t cb, int64_t ce) {
+      return ctx->q == 3 ? DgmWenoBatch<3>(ctx, u, w0, eps, tb, te, cb, ce) : DgmWenoBatch<4>(ctx, u, w0, eps, tb, te, cb, ce);
+    };
+    if (phase != 1) {
+      if (int s = batch(0, nl, 0, fi)) return s;
+    }
+    if (phase != 0) {   // the limited inner cells' Taylor forms are refreshed together with the ghosts'
+      if (int s = batch(0, fi, 0, 0)) return s;
+      if (int s = batch(nl, nc, fi, nl)) return s;
+    }
+    return MCFD_OK;
+  }
   if (phase < -1 || phase > 1) return Fail(ctx, MCFD_ERR_ARG, "phase must be -1 (both), 0 (inner cells) or 1 (inter cells)");
   const int m = ctx->q == 3 ? 10 : 20, rows = ctx->q == 3 ? ModalShape<2>::kBasRows : ModalShape<3>::kBasRows;
   if (!ctx->bas.p) {   // first use: per-cell orthonormal bases, built on the host like the reference does at set-up

@@ -1000,6 +1000,7 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
 
 void oracle_weno_lazy(void *h, double w0, double eps, double *u);
 void oracle_weno_eigen(void *h, double w0, double eps, double *u);
+void oracle_dgm_weno_lazy(void *h, double w0, double eps, double *u);
 void oracle_set_limiter(void *h, int on, double w0, double eps) {
   oracle_t *o = h;
   o->limited = on; o->weno_w0 = w0; o->weno_eps = eps;
@@ -1013,7 +1014,8 @@ void oracle_rk_update(void *h, int order, double t, double dt, double *u) {
   memcpy(u0, u, sizeof(double) * m);
 #define EULER_NEXT(tt, dst) do { oracle_residual(o, (tt), u, r); \
     for (int64_t i = 0; i < m; ++i) { r[i] *= dt; dst[i] = u[i] + r[i]; } } while (0)
-#define LIMIT() do { if (o->limited == 1) oracle_weno_lazy(o, o->weno_w0, o->weno_eps, u); \
+#define LIMIT() do { if (o->limited == 1 && o->scheme == 9) oracle_dgm_weno_lazy(o, o->weno_w0, o->weno_eps, u); \
+    else if (o->limited == 1) oracle_weno_lazy(o, o->weno_w0, o->weno_eps, u); \
     else if (o->limited == 2) oracle_weno_eigen(o, o->weno_w0, o->weno_eps, u); } while (0)
   if (order == 1) {
     EULER_NEXT(t, un); memcpy(u, un, sizeof(double) * m); LIMIT();
@@ -1810,4 +1812,87 @@ static void dgm_approximate(oracle_t *o, int field_kind, const double *prm, doub
       modal_basis_values(o, &g->basis[c], x, phi);
       for (int i = 0; i < m; ++i) for (int k = 0; k < 5; ++k) column[(c * m + i) * 5 + k] += val[k] * phi[i] * g->wgt[c * n + a];
     }
+}
+
+/* limiter::Reconstruct(part, weno::Lazy(w0, eps)) on Projection cells (single part): as oracle_weno_lazy, but the
+   modal coefficients are the state itself and every integral uses the cell's Gauss-Legendre rule */
+static double dgm_smoothness(const oracle_t *o, const dgm_t *g, int64_t c, const double *coef) {
+  int n = o->n, m = g->m;
+  const modal_basis_t *b = &g->basis[c];
+  double tc[MAXM], integral[MAXM] = {0};
+  for (int j = 0; j < m; ++j) {
+    double v = 0;
+    for (int i = j; i < m; ++i) v += coef[i] * b->s[i][j];
+    tc[j] = v;
+  }
+  for (int a = 0; a < n; ++a) {
+    double d[3], pdv[MAXM], w = g->wgt[c * n + a];
+    for (int k = 0; k < 3; ++k) d[k] = g->xyz[(c * n + a) * 3 + k] - b->center[k];
+    taylor_partial_derivatives(o->degree, d, tc, pdv);
+    for (int i = 0; i < m; ++i) integral[i] += pdv[i] * pdv[i] * w;
+  }
+  double volume = 1 / (b->s[0][0] * b->s[0][0]);
+  double total = (integral[1] + integral[2] + integral[3]) * (pow(volume, 1 * 2. / 3 - 1) / (tgamma(2) * tgamma(2)));
+  static const int begin[4] = {1, 4, 10, 20};
+  for (int p = 2; p <= o->degree; ++p) {
+    double sm = 0;
+    for (int i = begin[p - 1]; i < begin[p]; ++i) sm += integral[i];
+    total += sm * (pow(volume, p * 2. / 3 - 1) / (tgamma(p + 1) * tgamma(p + 1)));
+  }
+  return total;
+}
+void oracle_dgm_weno_lazy(void *h, double w0, double eps, double *u) {
+  oracle_t *o = h;
+  dgm_t *g = o->dgm;
+  int n = o->n, m = g->m;
+  int64_t nc = o->n_cells;
+  double *fresh = malloc(sizeof(double) * nc * 5 * m);
+  int *adj_cnt = calloc(nc, sizeof(int));
+  int64_t *adj = malloc(sizeof(int64_t) * nc * 6);
+  for (int64_t f = 0; f < o->n_interior; ++f) {
+    int64_t a = o->holder[f], b = o->sharer[f];
+    adj[a * 6 + adj_cnt[a]++] = b;
+    adj[b * 6 + adj_cnt[b]++] = a;
+  }
+  for (int64_t c = 0; c < nc; ++c) {
+    const modal_basis_t *mb = &g->basis[c];
+    int cnt = adj_cnt[c];
+    double cand[7][5][MAXM], mine[5][MAXM];
+    double s00 = mb->s[0][0];
+    for (int k = 0; k < 5; ++k) for (int i = 0; i < m; ++i) mine[k][i] = u[(c * m + i) * 5 + k];
+    for (int j = 0; j < cnt; ++j) {
+      int64_t d = adj[c * 6 + j];
+      memset(cand[j], 0, sizeof cand[j]);
+      for (int a = 0; a < n; ++a) {
+        double phi[MAXM], phn[MAXM], w = g->wgt[c * n + a];
+        const double *x = &g->xyz[(c * n + a) * 3];
+        modal_basis_values(o, mb, x, phi);
+        modal_basis_values(o, &g->basis[d], x, phn);
+        for (int k = 0; k < 5; ++k) {
+          double v = 0;
+          for (int i = 0; i < m; ++i) v += u[(d * m + i) * 5 + k] * phn[i];
+          for (int i = 0; i < m; ++i) cand[j][k][i] += v * phi[i] * w;
+        }
+      }
+      for (int k = 0; k < 5; ++k) cand[j][k][0] += (mine[k][0] * s00 - cand[j][k][0] * s00) / s00;
+    }
+    for (int k = 0; k < 5; ++k) for (int i = 0; i < m; ++i) cand[cnt][k][i] = mine[k][i];
+    for (int k = 0; k < 5; ++k) {
+      double wgt[7], sum = 0;
+      for (int j = 0; j <= cnt; ++j) {
+        double beta = dgm_smoothness(o, g, c, cand[j][k]) + eps;
+        double w = j < cnt ? w0 : w0 * (-cnt) + 1.0;
+        wgt[j] = w / (beta * beta);
+        sum += wgt[j];
+      }
+      for (int j = 0; j <= cnt; ++j) wgt[j] /= sum;
+      for (int i = 0; i < m; ++i) {
+        double v = cand[cnt][k][i] * wgt[cnt];
+        for (int j = 0; j < cnt; ++j) v += cand[j][k][i] * wgt[j];
+        fresh[(c * m + i) * 5 + k] = v;
+      }
+    }
+  }
+  memcpy(u, fresh, sizeof(double) * nc * 5 * m);
+  free(fresh); free(adj_cnt); free(adj);
 }

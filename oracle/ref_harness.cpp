@@ -857,6 +857,12 @@ static SolverBase *Create(int scheme, int riemann, GlobalMesh &&mesh) {
     case 0: return new SolverImpl<sp::WithLimiter<sp::fr::Lobatto<ModalPart, RExact>, mini::limiter::weno::Eigen<Cell, RExact>>>(std::move(mesh));
     case 1: return new SolverImpl<sp::WithLimiter<sp::fr::Lobatto<ModalPart, RHllc>, mini::limiter::weno::Eigen<Cell, RHllc>>>(std::move(mesh));
     }
+  } else if (scheme == 10) {  // WithLimiter<dg::General, weno::Lazy> on Projection cells: the reference's DGFEM + LIMITER build
+    using Lazy = mini::limiter::weno::Lazy<typename DgPart::Cell>;
+    switch (riemann) {
+    case 0: return new SolverImpl<sp::WithLimiter<sp::dg::General<DgPart, RExact>, Lazy>>(std::move(mesh));
+    case 1: return new SolverImpl<sp::WithLimiter<sp::dg::General<DgPart, RHllc>, Lazy>>(std::move(mesh));
+    }
   } else if (scheme == 9) {   // dg::General<Part<Projection>, Riemann>
     switch (riemann) {
     case 0: return new SolverImpl<sp::dg::General<DgPart, RExact>>(std::move(mesh));

@@ -87,6 +87,19 @@ def main():
         np.savez_compressed(os.path.join(HERE, name + ".npz"), projected=projected, u=u, residual=res, dt=dt,
                             u_rk3=r.get_solution(), nodes=m.nodes, cells=m.cells, bfaces=m.bfaces, btags=m.btags)
         print(name, np.linalg.norm(res), dt)
+    # WithLimiter<dg::General<Part<Projection>>, weno::Lazy>: demo/euler/sourceless.hpp under DGFEM + LIMITER
+    for name, degree, riemann in cases.DGM_WENO_GOLDEN_CASES:
+        r = refapi.Ref(m, degree=degree, scheme=refapi.DG_GENERAL_WENO_LAZY, riemann=riemann, weno=cases.WENO)
+        cases.apply_bcs_ref(r)
+        r.approximate(refapi.F_SMOOTH, [1.0])
+        base = r.get_solution()
+        u = base * (1 + 5e-2 * np.random.default_rng(degree).uniform(-1, 1, base.shape))
+        r.set_solution_all(u)
+        limited = r.get_solution()
+        r.rk_update(3, 0.0, cases.GOLDEN_DT, 1)
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), u=u, limited=limited, u_rk3=r.get_solution(),
+                            nodes=m.nodes, cells=m.cells, bfaces=m.bfaces, btags=m.btags)
+        print(name, np.abs(limited - u).max())
     # WithLimiter<fr::Lobatto, weno::Lazy>: the limiter's action on a column, and an RK3 step with it
     for name, degree, riemann in cases.WENO_GOLDEN_CASES:
         r = refapi.Ref(m, degree=degree, scheme=refapi.FR_WENO_LAZY, riemann=riemann, weno=cases.WENO)

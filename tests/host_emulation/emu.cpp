@@ -141,6 +141,7 @@ static void RunWeno(HostMesh const &mesh, std::vector<double> &u, std::vector<do
   WenoArgs a;
   a.u = u.data(); a.geom = geom.data(); a.bas = bas.data(); a.h2s = h2s.data(); a.nbr = nbr.data(); a.code = code.data();
   a.mod = mod.data(); a.tay = tay.data(); a.mod_new = modn.data(); a.tay_new = tayn.data(); a.w0 = w0; a.eps = eps;
+  a.comp_stride = M; a.mode_stride = 1; a.modal_state = 0; a.legendre = 0;
   std::vector<double> scratch((size_t)(7 * 5 * M + 5 * M) * kTile, 0.0);
   auto limit_eigen_tile = [&](int64_t t) {   // WenoEigenKernel's phases, thread by thread
     WenoEigenArgs e;

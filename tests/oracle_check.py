@@ -124,7 +124,8 @@ class Oracle:
 
     def weno_lazy(self, u, w0=0.001, eps=1e-6):
         u = np.array(u, dtype=np.float64, copy=True)
-        lib().oracle_weno_lazy(self.h, C.c_double(w0), C.c_double(eps), _dp(u))
+        f = lib().oracle_dgm_weno_lazy if self.kfields in (50, 100) else lib().oracle_weno_lazy
+        f(self.h, C.c_double(w0), C.c_double(eps), _dp(u))
         return u
 
     def time_step(self, u, dt_guess, rk_order):

@@ -12,7 +12,7 @@ _libs: dict[int, C.CDLL] = {}
 
 CB = C.CFUNCTYPE(None, C.c_int, C.POINTER(C.c_double), C.c_double, C.POINTER(C.c_double), C.c_void_p)
 
-FR, DG, FR_GENERAL, FR_VISCOUS, FR_WENO_LAZY, FR_WENO_EIGEN, FR_ISOTROPIC, FR_ENERGY_VISCOSITY, FR_GENERAL_VISCOUS, DG_GENERAL = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9
+FR, DG, FR_GENERAL, FR_VISCOUS, FR_WENO_LAZY, FR_WENO_EIGEN, FR_ISOTROPIC, FR_ENERGY_VISCOSITY, FR_GENERAL_VISCOUS, DG_GENERAL, DG_GENERAL_WENO_LAZY = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10
 EXACT, HLLC, AUSM = 0, 1, 2
 # boundary kinds, order of fem.hpp:196-222 as used by ref_harness.cpp
 WALL, SUPERSONIC_OUTLET, SUPERSONIC_INLET, SUBSONIC_INLET, SUBSONIC_OUTLET, SMART, NO_SLIP = range(7)
@@ -50,7 +50,7 @@ class Ref:
         self.pre = f"ref_p{degree}_"
         self.n_nodes_per_cell = (degree + 1) ** 3
         self.kfields = 5 * self.n_nodes_per_cell
-        if scheme == 9:   # dg::General on Projection: K x M modal coefficients per cell
+        if scheme in (9, 10):   # dg::General on Projection: K x M modal coefficients per cell
             self.kfields = 5 * {2: 10, 3: 20}[degree]
         self._f("set_vincent")(C.c_double(c_next))
         self._f("set_weno")(C.c_double(weno[0]), C.c_double(weno[1]))

@@ -122,3 +122,51 @@ def test_dg_general_two_parts_with_halo_buffers():
             sp.ctx.rk_stage_inter(stage)
     for sp, p in zip(S, P):
         assert relerr(sp.GetSolutionColumn().reshape(-1, 50), expect_u[p.local_global]) < TOL
+
+
+@pytest.mark.parametrize("name,degree,riemann", cases.DGM_WENO_GOLDEN_CASES)
+def test_dg_general_with_weno_lazy_golden(name, degree, riemann):
+    """WithLimiter<dg::General<Part<Projection>>, weno::Lazy>: the reference's DGFEM + LIMITER build."""
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    m = meshmod.HexMesh(nodes=g["nodes"], cells=g["cells"], bfaces=g["bfaces"], btags=g["btags"])
+    sp = Spatial(Part(m), scheme=capi.DG_GENERAL, degree=degree, riemann=riemann, device=0)
+    cases.apply_bcs_spatial(sp, cases.MIXED_BCS)
+    sp.SetLimiter(*cases.WENO)
+    sp.SetSolutionColumn(g["u"])
+    assert relerr(sp.GetSolutionColumn(), g["limited"]) < TOL
+    RungeKutta(3).Update(sp, 0.0, cases.GOLDEN_DT)
+    assert relerr(sp.GetSolutionColumn(), g["u_rk3"]) < TOL
+
+
+def test_dg_general_weno_two_parts_match_the_reference_parts():
+    import refapi
+    import torch
+    from minicfd_b200.halo import _DeviceArray
+    if not refapi.available(2):
+        pytest.skip("oracle/_ref not shipped")
+    m = meshmod.scramble(meshmod.box(6, 4, 2, warp=0.1, seed=2), seed=3)
+    parts = (np.arange(m.n_cells) * 2 // m.n_cells).astype(np.int32)
+    o = oc.Oracle(m, 2, 9, 1)
+    u = o.approximate(oc.F_SMOOTH, [1.0])
+    u = u * (1 + 5e-2 * np.random.default_rng(2).uniform(-1, 1, u.shape))
+    r = refapi.Ref(m, degree=2, scheme=refapi.DG_GENERAL_WENO_LAZY, riemann=1, cell_parts=parts, n_parts=2, weno=cases.WENO)
+    P = [Part(m, parts, k, 2) for k in range(2)]
+    r.set_solution_all([p.gather_from_global(u, 50) for p in P])
+    S = [Spatial(p, scheme=capi.DG_GENERAL, degree=2, riemann=capi.HLLC, device=0) for p in P]
+    bufs = [sum(sp.ctx.halo_buffers(), ()) for sp in S]
+    for sp, p in zip(S, P):
+        sp.ctx.set_solution(p.gather_from_global(u, 50))
+    for sp in S:
+        sp.ctx.halo_pack()
+    torch.cuda.synchronize()
+    for a, b in ((0, 1), (1, 0)):
+        src = torch.as_tensor(_DeviceArray(bufs[a][0], bufs[a][1]), device="cuda")
+        dst = torch.as_tensor(_DeviceArray(bufs[b][2], bufs[b][3]), device="cuda")
+        dst.copy_(src)
+    torch.cuda.synchronize()
+    for sp in S:
+        sp.ctx.limiter_weno_lazy(*cases.WENO, 0)
+        sp.ctx.halo_unpack()
+        sp.ctx.limiter_weno_lazy(*cases.WENO, 1)
+    for k, sp in enumerate(S):
+        assert relerr(sp.GetSolutionColumn(), r.get_solution(k)) < TOL

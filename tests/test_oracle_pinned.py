@@ -222,6 +222,18 @@ def test_c_oracle_dg_general_matches_golden(name, degree, riemann):
     assert relerr(o.rk_update(g["u"], 3, 0.0, cases.GOLDEN_DT), g["u_rk3"]) < TOL
 
 
+@pytest.mark.parametrize("name,degree,riemann", cases.DGM_WENO_GOLDEN_CASES)
+def test_c_oracle_dg_general_weno_lazy_matches_golden(name, degree, riemann):
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    o = oc.Oracle(_golden_mesh(g), degree, 9, riemann)
+    cases.apply_bcs_oracle(o)
+    limited = o.weno_lazy(g["u"], *cases.WENO)
+    assert relerr(limited, g["limited"]) < TOL
+    assert np.abs(g["limited"] - g["u"]).max() > 1e-7
+    o.set_limiter(*cases.WENO)
+    assert relerr(o.rk_update(limited, 3, 0.0, cases.GOLDEN_DT), g["u_rk3"]) < TOL
+
+
 def _flux_1d(rho, u, p):
     """Flux of a 1-D primitive state (test/riemann/euler/exact.cpp:34-39)."""
     e = p / 0.4 + 0.5 * rho * u * u
