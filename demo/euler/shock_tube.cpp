@@ -33,18 +33,17 @@ constexpr int kDegrees = 2;
 using Gx = mini::integrator::Legendre<Scalar, kDegrees + 1>;
 #include "mini/polynomial/projection.hpp"
 using Polynomial = mini::polynomial::Projection<Scalar, kDimensions, kDegrees, kComponents>;
-#else
+#else          // demo/euler/sourceless.hpp:35-49
 #include "mini/integrator/lobatto.hpp"
 using Gx = mini::integrator::Lobatto<Scalar, kDegrees + 1>;
 #include "mini/polynomial/hexahedron.hpp"
 using Interpolation = mini::polynomial::Hexahedron<Gx, Gx, Gx, kComponents, false>;
-#endif
-#ifdef DGFEM
-#elif defined(LIMITER)   // demo/euler/sourceless.hpp:41-47
+#ifdef LIMITER
 #include "mini/polynomial/extrapolation.hpp"
 using Polynomial = mini::polynomial::Extrapolation<Interpolation>;
 #else
 using Polynomial = Interpolation;
+#endif
 #endif
 #include "mini/mesh/part.hpp"
 using Part = mini::mesh::part::Part<int64_t, Polynomial>;
@@ -52,11 +51,14 @@ using Cell = typename Part::Cell;
 using Global = typename Part::Global;
 using Value = typename Part::Value;
 #include "mini/spatial/fr/lobatto.hpp"
-#ifdef DGFEM     // demo/euler/sourceless.hpp:64-66 (without the limiter)
 #include "mini/spatial/dg/general.hpp"
-using Spatial = mini::spatial::dg::General<Part, Riemann>;
-#elif defined(LIMITER)   // demo/euler/sourceless.hpp:60-80
-using General = mini::spatial::fr::Lobatto<Part, Riemann>;
+#ifdef DGFEM     // demo/euler/sourceless.hpp:62-74
+using Unlimited = mini::spatial::dg::General<Part, Riemann>;
+#else
+using Unlimited = mini::spatial::fr::Lobatto<Part, Riemann>;
+#endif
+#ifdef LIMITER   // demo/euler/sourceless.hpp:76-80
+using General = Unlimited;
 #include "mini/limiter/weno.hpp"
 #include "mini/limiter/reconstruct.hpp"
 #include "mini/spatial/with_limiter.hpp"
@@ -67,7 +69,7 @@ using Limiter = mini::limiter::weno::Lazy<Cell>;
 #endif
 using Spatial = mini::spatial::WithLimiter<General, Limiter>;
 #else
-using Spatial = mini::spatial::fr::Lobatto<Part, Riemann>;
+using Spatial = Unlimited;
 #endif
 #include "mini/temporal/rk.hpp"
 constexpr int kOrders = 3;

@@ -102,13 +102,13 @@ def test_sod_driver_with_weno_limiter_through_cpp_template_api(tmp_path, eigen):
     assert np.abs(got - ref).max() / np.abs(ref).max() < 1e-11
 
 
-def _sod_dgfem_reference(n_steps):
-    """Sod with dg::General on the modal polynomial (the reference's DGFEM build), HLLC."""
+def _sod_dgfem_reference(n_steps, limiter=False):
+    """Sod with dg::General on the modal polynomial (the reference's DGFEM build, optionally + LIMITER), HLLC."""
     m = meshmod.box(50, 2, 3, hi=(5.0, 0.2, 0.3))
     left = np.array([1.0, 0, 0, 0, 1.0 / 0.4]); right = np.array([0.125, 0, 0, 0, 0.1 / 0.4])
     dt_max = 0.2 / 200
     if refapi.available(2):
-        r = refapi.Ref(m, degree=2, scheme=refapi.DG_GENERAL, riemann=1)
+        r = refapi.Ref(m, degree=2, scheme=refapi.DG_GENERAL_WENO_LAZY if limiter else refapi.DG_GENERAL, riemann=1)
         def ic(tag, xyz, t, out, user):
             v = left if xyz[0] < 2.5 else right
             for k in range(5):
@@ -127,14 +127,16 @@ def _sod_dgfem_reference(n_steps):
     return None
 
 
-def test_sod_driver_dgfem_through_cpp_template_api(tmp_path):
-    """-DDGFEM: Legendre rules, the modal Projection polynomial and dg::General as demo/euler/sourceless.hpp:28-33,
-    64-66 name them; Approximate is the L2 projection at the Gauss points."""
-    ref = _sod_dgfem_reference(10)
+@pytest.mark.parametrize("limiter", [False, True])
+def test_sod_driver_dgfem_through_cpp_template_api(tmp_path, limiter):
+    """-DDGFEM [-DLIMITER]: Legendre rules, the modal Projection polynomial, dg::General and WithLimiter<..,
+    weno::Lazy<Cell>> as demo/euler/sourceless.hpp:28-33, 62-80 name them; Approximate is the L2 projection at the
+    Gauss points (followed by the limiter)."""
+    ref = _sod_dgfem_reference(10, limiter)
     if ref is None:
         pytest.skip("oracle/_ref not shipped")
     exe = tmp_path / "shock_tube_dgfem"
-    subprocess.check_call(["g++", "-DUSE_HLLC", "-DDGFEM", "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"),
+    subprocess.check_call(["g++", "-DUSE_HLLC", "-DDGFEM", *(["-DLIMITER"] if limiter else []), "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"),
                            os.path.join(ROOT, "demo", "euler", "shock_tube.cpp"), "-o", str(exe),
                            "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200",
                            "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")])
@@ -143,7 +145,7 @@ def test_sod_driver_dgfem_through_cpp_template_api(tmp_path):
     assert res.returncode == 0, res.stdout + res.stderr
     got = np.fromfile(out, dtype=np.float64)
     assert got.shape == ref.shape == (300 * 50,)
-    assert np.abs(got - ref).max() / np.abs(ref).max() < 1e-12
+    assert np.abs(got - ref).max() / np.abs(ref).max() < (1e-11 if limiter else 1e-12)
 
 
 def _cavity_reference(n, n_steps):
