@@ -394,6 +394,9 @@ typedef struct oracle_s {
   double beta0, beta1, nu, prandtl;    /* direct.hpp:31-32, navier_stokes.hpp:54 (class statics there) */
   double d2[MAXQ][MAXQ];               /* d2[i][m] = l_m''(x_i) */
   double *jtgrad;   /* [cell][n][3][3][3] d(J^-T)/d(xi_a) = mat_after_grad_of_U_, hexahedron.hpp:233-236 */
+  double *djac;     /* [cell][n][3][3][3] dJ/d(xi_a), coordinate/cell.hpp:100-119 */
+  double *d2jac;    /* [cell][3] the one non-zero row of d2J/d(xi_a)d(xi_b), a != b (row 3-a-b): sum_v s_v P_v / 8 */
+  int klocal;       /* Hexahedron<..., true>: a column holds det(J) u (polynomial/hexahedron.hpp:338-343) */
   double *dist;     /* [face][q*q] normal . HolderToSharer, fem.hpp:83-85 */
   /* scheme 9 = dg::General on the modal Projection polynomial with Gauss-Legendre rules */
   int kf;           /* doubles per cell in a column: 5 n (nodal) or 5 M (modal) */
@@ -491,6 +494,11 @@ void *oracle_create(int degree, int scheme, int riemann, int64_t n_nodes, const 
   o->det = malloc(sizeof(double) * n_cells * n);
   o->length = malloc(sizeof(double) * n_cells);
   o->jtgrad = malloc(sizeof(double) * n_cells * n * 27);
+  o->djac = malloc(sizeof(double) * n_cells * n * 27);
+  o->d2jac = calloc(n_cells * 3, sizeof(double));
+  for (int64_t c = 0; c < n_cells; ++c)
+    for (int v = 0; v < 8; ++v) for (int k = 0; k < 3; ++k)
+      o->d2jac[c * 3 + k] += VERT[v][0] * VERT[v][1] * VERT[v][2] / 8 * nodes[cn[c * 8 + v] * 3 + k];
   for (int i = 0; i < q; ++i) for (int m = 0; m < q; ++m) o->d2[i][m] = lagrange_d2(q, o->x, m, i);
   o->beta0 = 2.0; o->beta1 = 1.0 / 12; o->nu = 0.0; o->prandtl = 0.708;
   for (int64_t c = 0; c < n_cells; ++c) {
@@ -524,6 +532,7 @@ void *oracle_create(int degree, int scheme, int riemann, int64_t n_nodes, const 
       }
       for (int k = 0; k < 9; ++k) js[k] = det * inv[k]; /* polynomial/hexahedron.hpp:228-230 */
       o->det[c * n + a] = det;
+      memcpy(&o->djac[(c * n + a) * 27], dJ, sizeof dJ);
       for (int e = 0; e < 3; ++e) { /* -(J^-1 dJ_e J^-1)^T, polynomial/hexahedron.hpp:233-236 */
         double t1[3][3], t2[3][3];
         for (int r = 0; r < 3; ++r) for (int s2 = 0; s2 < 3; ++s2) {
@@ -634,7 +643,7 @@ void *oracle_create(int degree, int scheme, int riemann, int64_t n_nodes, const 
 void oracle_destroy(void *h) {
   oracle_t *o = h;
   dgm_free(o);
-  free(o->cell_nu); free(o->jtgrad); free(o->dist); free(o->xyz); free(o->jstar); free(o->jinv); free(o->det); free(o->length); free(o->holder); free(o->sharer);
+  free(o->djac); free(o->d2jac); free(o->cell_nu); free(o->jtgrad); free(o->dist); free(o->xyz); free(o->jstar); free(o->jinv); free(o->det); free(o->length); free(o->holder); free(o->sharer);
   free(o->tag); free(o->h_node); free(o->s_node); free(o->h_dir); free(o->s_dir); free(o->h_scale);
   free(o->s_scale); free(o->frame); free(o->fweight); free(o->fxyz); free(o);
 }
@@ -648,6 +657,11 @@ void oracle_set_cell_viscosity(void *h, const double *nu) { /* [n_cells][5], or 
     o->cell_nu = malloc(sizeof(double) * o->n_cells * 5);
     memcpy(o->cell_nu, nu, sizeof(double) * o->n_cells * 5);
   }
+}
+void oracle_set_local(void *h, int klocal) { ((oracle_t *)h)->klocal = klocal; }
+void oracle_node_determinants(void *h, double *det) {
+  oracle_t *o = h;
+  memcpy(det, o->det, sizeof(double) * o->n_cells * o->n);
 }
 void oracle_set_viscous(void *h, double beta0, double beta1, double nu, double prandtl) {
   oracle_t *o = h;
@@ -730,6 +744,92 @@ static void global_gradient_hessian(const oracle_t *o, const double *u, int64_t 
     }
     for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j)
       G[i][j] = inv[i * 3] * S[0][j] + inv[i * 3 + 1] * S[1][j] + inv[i * 3 + 2] * S[2][j];
+    H[0][k] = G[0][0]; H[1][k] = G[0][1]; H[2][k] = G[0][2]; H[3][k] = G[1][1]; H[4][k] = G[1][2]; H[5][k] = G[2][2];
+  }
+}
+/* ---- kLocal == true (polynomial/hexahedron.hpp:171-219, 397-408, 526-562): U = det(J) u are the coefficients ---- */
+typedef struct {
+  double det, dg[3];       /* det J and its local gradient (coordinate/cell.hpp:157-167) */
+  double mah[3][3];        /* mat_after_hess_of_U_ = J^-T / det */
+  double mag[3][3][3];     /* mat_after_grad_of_U_[a] */
+  double mbg[3];           /* mat_before_grad_of_U_ */
+  double mbu[3][3];        /* mat_before_U_ */
+} local_cache_t;
+static void local_cache(const oracle_t *o, int64_t c, int a, local_cache_t *L) {
+  int n = o->n;
+  const double *inv = &o->jinv[(c * n + a) * 9], *tg = &o->jtgrad[(c * n + a) * 27], *dJ = &o->djac[(c * n + a) * 27];
+  double det = o->det[c * n + a], det2 = det * det, det3 = det2 * det;
+  double P[3][3][3], tr[3], dh[3][3];   /* P[e] = inv dJ_e */
+  for (int e = 0; e < 3; ++e) {
+    tr[e] = 0;
+    for (int r = 0; r < 3; ++r) for (int s2 = 0; s2 < 3; ++s2) {
+      double v = 0;
+      for (int m = 0; m < 3; ++m) v += inv[r * 3 + m] * dJ[e * 9 + m * 3 + s2];
+      P[e][r][s2] = v;
+    }
+    for (int r = 0; r < 3; ++r) tr[e] += P[e][r][r];
+    L->dg[e] = det * tr[e];
+  }
+  for (int e = 0; e < 3; ++e) for (int f = 0; f < 3; ++f) { /* coordinate/cell.hpp:174-199 */
+    double t2 = 0, tpp = 0;
+    if (e != f) { int p = 3 - e - f; for (int x = 0; x < 3; ++x) t2 += inv[x * 3 + p] * o->d2jac[c * 3 + x]; }
+    for (int r = 0; r < 3; ++r) for (int m = 0; m < 3; ++m) tpp += P[e][r][m] * P[f][m][r];
+    dh[e][f] = (t2 + tr[e] * tr[f] - tpp) * det;
+  }
+  L->det = det;
+  for (int b = 0; b < 3; ++b) for (int j = 0; j < 3; ++j) L->mah[b][j] = inv[j * 3 + b] / det;   /* inv_T(b, j) = inv(j, b) */
+  for (int e = 0; e < 3; ++e) for (int b = 0; b < 3; ++b) for (int j = 0; j < 3; ++j)
+    L->mag[e][b][j] = tg[e * 9 + b * 3 + j] / det + inv[j * 3 + b] * (-L->dg[e] / det2);
+  for (int j = 0; j < 3; ++j) {
+    double v = 0;
+    for (int b = 0; b < 3; ++b) v += L->dg[b] * inv[j * 3 + b];
+    L->mbg[j] = v / det2;
+  }
+  for (int e = 0; e < 3; ++e) for (int j = 0; j < 3; ++j) {
+    double v = 0;
+    for (int b = 0; b < 3; ++b) v += dh[e][b] * (inv[j * 3 + b] / det2);
+    for (int b = 0; b < 3; ++b) v += L->dg[b] * (tg[e * 9 + b * 3 + j] / det2 + inv[j * 3 + b] * (-2 * L->dg[e] / det3));
+    L->mbu[e][j] = v;
+  }
+}
+/* GetGlobalValueGradient / GetGlobalValueGradientHessian for kLocal == true; U is the column, val = U / det */
+static void local_gradient_hessian(const oracle_t *o, const double *U, int64_t c, int a, double *val, double g[3][5],
+    double H[6][5]) {
+  int n = o->n;
+  const double *inv = &o->jinv[(c * n + a) * 9];
+  local_cache_t L;
+  local_cache(o, c, a, &L);
+  double lg[3][5], lh[6][5];
+  memset(lg, 0, sizeof lg); memset(lh, 0, sizeof lh);
+  for (int b = 0; b < n; ++b) {
+    double bg[3], bh[6];
+    basis_local_gradient(o, a, b, bg); basis_local_hessian(o, a, b, bh);
+    for (int k = 0; k < 5; ++k) {
+      double ub = U[(c * n + b) * 5 + k];
+      for (int x = 0; x < 3; ++x) lg[x][k] += bg[x] * ub;
+      for (int x = 0; x < 6; ++x) lh[x][k] += bh[x] * ub;
+    }
+  }
+  for (int k = 0; k < 5; ++k) val[k] = U[(c * n + a) * 5 + k] / L.det;
+  for (int k = 0; k < 5; ++k) { /* hexahedron.hpp:397-408: J* (grad_local U - grad det u) / det^2 */
+    double vg[3];
+    for (int e = 0; e < 3; ++e) vg[e] = (lg[e][k] - L.dg[e] * val[k]) / (L.det * L.det);
+    for (int x = 0; x < 3; ++x) g[x][k] = (L.det * inv[x * 3]) * vg[0] + (L.det * inv[x * 3 + 1]) * vg[1] + (L.det * inv[x * 3 + 2]) * vg[2];
+  }
+  if (!H) return;
+  static const int SYM[3][3] = {{0, 1, 2}, {1, 3, 4}, {2, 4, 5}};
+  for (int k = 0; k < 5; ++k) { /* hexahedron.hpp:526-562 */
+    double S[3][3], G[3][3];
+    for (int e = 0; e < 3; ++e) for (int j = 0; j < 3; ++j) {
+      double v = 0;
+      for (int b = 0; b < 3; ++b) v += lh[SYM[e][b]][k] * L.mah[b][j];
+      for (int b = 0; b < 3; ++b) v += lg[b][k] * L.mag[e][b][j];
+      v -= L.mbg[j] * lg[e][k];
+      v -= L.mbu[e][j] * U[(c * n + a) * 5 + k];
+      S[e][j] = v;
+    }
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j)
+      G[i][j] = ((L.det * inv[i * 3]) * S[0][j] + (L.det * inv[i * 3 + 1]) * S[1][j] + (L.det * inv[i * 3 + 2]) * S[2][j]) / L.det;
     H[0][k] = G[0][0]; H[1][k] = G[0][1]; H[2][k] = G[0][2]; H[3][k] = G[1][1]; H[4][k] = G[1][2]; H[5][k] = G[2][2];
   }
 }
@@ -829,11 +929,20 @@ static void ddg_common_gradient(const oracle_t *o, double dist, const double *nr
     gc[x][k] += n1[y] * (hr[SYM[x][y]][k] - hl[SYM[x][y]][k]);
 }
 
-void oracle_residual(void *h, double t, const double *u, double *res) {
+void oracle_residual(void *h, double t, const double *column, double *res) {
   oracle_t *o = h;
-  if (o->scheme == 9) { dgm_residual(o, t, u, res); return; }
+  if (o->scheme == 9) { dgm_residual(o, t, column, res); return; }
   int q = o->q, n = o->n, fq = q * q, K = 5;
   int64_t nc = o->n_cells;
+  /* kLocal == true: the column holds U = det u; values are U / det (hexahedron.hpp:338-340), gradients and
+     Hessians come from U's interpolant, the residual is dU/dt and is not divided by det (fr/general.hpp:251-253) */
+  const double *U = column, *u = column;
+  double *values = NULL;
+  if (o->klocal) {
+    values = malloc(sizeof(double) * nc * n * K);
+    for (int64_t i = 0; i < nc * n; ++i) for (int k = 0; k < K; ++k) values[i * K + k] = U[i * K + k] / o->det[i];
+    u = values;
+  }
   double *fhat = malloc(sizeof(double) * nc * n * 15); /* flux_matrices_ cache, fr/general.hpp:213-215 */
   memset(res, 0, sizeof(double) * nc * n * K);
   for (int64_t c = 0; c < nc; ++c) {
@@ -841,8 +950,9 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
       double F[5][3];
       flux_matrix(&u[(c * n + a) * K], F);
       if (IS_NS(o) || o->scheme == 6) { /* fem.hpp:397-404 */
-        double gc[3][5];
-        global_gradient(o, u, c, a, gc);
+        double gc[3][5], vdummy[5];
+        if (o->klocal) local_gradient_hessian(o, U, c, a, vdummy, gc, NULL);
+        else global_gradient(o, u, c, a, gc);
         if (IS_NS(o)) {
           ns_minus_flux_matrix(o, F, &u[(c * n + a) * K], gc);
         } else {
@@ -897,8 +1007,14 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
         if (IS_NS(o) || o->scheme == 6) { /* fr/general.hpp:316-350 */
           const double *us = &u[(cs * n + as) * K];
           double gh_[3][5], gs_[3][5], hh[6][5], hs[6][5], gcm[3][5], ucm[5];
-          global_gradient_hessian(o, u, ch, ah, gh_, hh);
-          global_gradient_hessian(o, u, cs, as, gs_, hs);
+          if (o->klocal) {
+            double vd[5];
+            local_gradient_hessian(o, U, ch, ah, vd, gh_, hh);
+            local_gradient_hessian(o, U, cs, as, vd, gs_, hs);
+          } else {
+            global_gradient_hessian(o, u, ch, ah, gh_, hh);
+            global_gradient_hessian(o, u, cs, as, gs_, hs);
+          }
           ddg_common_gradient(o, o->dist[f * fq + p], fr->a, uh, us, gh_, gs_, hh, hs, gcm);
           for (int k = 0; k < 5; ++k) ucm[k] = (uh[k] + us[k]) / 2;
           if (IS_NS(o)) {
@@ -955,7 +1071,8 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
           if ((!IS_NS(o) && o->scheme != 6) || IS_GENERAL(o)) continue;
           double gh_[3][5];
           boundary_flux(o->riemann, 0, fr, uh, given, fu);
-          global_gradient(o, u, ch, ah, gh_);
+          if (o->klocal) { double vd[5]; local_gradient_hessian(o, U, ch, ah, vd, gh_, NULL); }
+          else global_gradient(o, u, ch, ah, gh_);
           if (IS_NS(o)) {
             ns_minus_flux_no_slip(o, fu, given, uh, gh_, fr->a, o->beta0 / o->dist[f * fq + p]);
           } else { /* linear.hpp:85-91: the plain normal flux of the cell's own gradient */
@@ -991,6 +1108,7 @@ void oracle_residual(void *h, double t, const double *u, double *res) {
   for (int64_t c = 0; c < nc; ++c)
     for (int a = 0; a < n; ++a) {
       int ia[3] = {a / fq, (a / q) % q, a % q};
+      if (o->klocal) continue;
       double s = o->scheme != 1 ? 1.0 / o->det[c * n + a] /* fr/general.hpp:256-266 */
           : 1.0 / (o->w[ia[0]] * o->w[ia[1]] * o->w[ia[2]] * o->det[c * n + a]); /* dg/lobatto.hpp:143-158 */
       for (int k = 0; k < 5; ++k) res[(c * n + a) * K + k] *= s;
@@ -1053,7 +1171,9 @@ double oracle_time_step(void *h, const double *u, double dt_guess, int rk_order)
   for (int64_t c = 0; c < o->n_cells; ++c) {
     double vmax = 1e-5;
     for (int a = 0; a < o->n; ++a) {
-      prim_t q = cons_to_prim(&u[(c * o->n + a) * 5]);
+      double val[5];
+      for (int k = 0; k < 5; ++k) val[k] = o->klocal ? u[(c * o->n + a) * 5 + k] / o->det[c * o->n + a] : u[(c * o->n + a) * 5 + k];
+      prim_t q = cons_to_prim(val);
       double cs = sound_speed(q.rho, q.p), v = sqrt(q.u * q.u + q.v * q.v + q.w * q.w);
       double s = cs + v > cs - v ? cs + v : cs - v;
       if (s > vmax) vmax = s;

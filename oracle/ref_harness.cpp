@@ -819,6 +819,13 @@ using Energy = mini::spatial::EnergyBasedViscosity<Part, IsoViscous<Unrotated>>;
 using EExact = Energy<mini::riemann::euler::Exact<Gas, 3>>;
 using EHllc = Energy<mini::riemann::euler::HartenLaxLeerContact<Gas, 3>>;
 
+// the kLocal == true expansion (coefficients = det(J) u), as the reference's laminar drivers use it for FR
+// (demo/laminar/shockless.hpp:62-69)
+using PolyL = mini::polynomial::Hexahedron<Gx, Gx, Gx, 5, true>;
+using PartL = OraclePart<PolyL>;
+template <class Unrotated>
+using ViscousL = Viscous<Unrotated>;
+
 // modal DG on the stand-alone Projection polynomial with Gauss-Legendre rules (demo/euler/sourceless.hpp:28-33, 64-66)
 using DgPart = OraclePart<ModalDgPoly>;
 
@@ -856,6 +863,18 @@ static SolverBase *Create(int scheme, int riemann, GlobalMesh &&mesh) {
     switch (riemann) {
     case 0: return new SolverImpl<sp::WithLimiter<sp::fr::Lobatto<ModalPart, RExact>, mini::limiter::weno::Eigen<Cell, RExact>>>(std::move(mesh));
     case 1: return new SolverImpl<sp::WithLimiter<sp::fr::Lobatto<ModalPart, RHllc>, mini::limiter::weno::Eigen<Cell, RHllc>>>(std::move(mesh));
+    }
+  } else if (scheme == 11) {  // fr::Lobatto on Hexahedron<..., true>, Euler
+    switch (riemann) {
+    case 0: return new SolverImpl<sp::fr::Lobatto<PartL, RExact>>(std::move(mesh));
+    case 1: return new SolverImpl<sp::fr::Lobatto<PartL, RHllc>>(std::move(mesh));
+    case 2: return new SolverImpl<sp::fr::Lobatto<PartL, RAusm>>(std::move(mesh));
+    }
+  } else if (scheme == 12) {  // ... Navier-Stokes + direct DG: demo/laminar/shockless.hpp as shipped
+    switch (riemann) {
+    case 0: return new SolverImpl<sp::fr::Lobatto<PartL, VExact>>(std::move(mesh));
+    case 1: return new SolverImpl<sp::fr::Lobatto<PartL, VHllc>>(std::move(mesh));
+    case 2: return new SolverImpl<sp::fr::Lobatto<PartL, VAusm>>(std::move(mesh));
     }
   } else if (scheme == 10) {  // WithLimiter<dg::General, weno::Lazy> on Projection cells: the reference's DGFEM + LIMITER build
     using Lazy = mini::limiter::weno::Lazy<typename DgPart::Cell>;

@@ -56,6 +56,19 @@ class Oracle:
         except Exception:
             pass
 
+    def set_local(self, klocal=True):
+        """Hexahedron<..., true>: columns hold det(J) u"""
+        lib().oracle_set_local(self.h, C.c_int(1 if klocal else 0))
+
+    def jacobian_determinants(self):
+        """det J at the nodes, [n_cells][N]: U = det u"""
+        self.set_local(False)
+        ones = np.ones(self.n_cells * self.kfields)
+        n = self.kfields // 5
+        out = np.empty((self.n_cells, n))
+        lib().oracle_node_determinants(self.h, _dp(out))
+        return out
+
     def set_viscous(self, beta0, beta1, nu, prandtl):
         lib().oracle_set_viscous(self.h, C.c_double(beta0), C.c_double(beta1), C.c_double(nu), C.c_double(prandtl))
 
