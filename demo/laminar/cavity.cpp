@@ -3,7 +3,7 @@
 // with the GPU path selected by the include directory alone:
 //     g++ -std=c++20 -I include demo/laminar/cavity.cpp -L minicfd_b200 -lminicfd_b200
 // Differences from the reference driver: the mesh is a structured box built in memory (gmsh -> CGNS -> METIS is
-// out of scope), there is no JSON / CGNS / VTK I/O, and the expansion is the kLocal == false one.
+// out of scope) and there is no JSON / CGNS / VTK I/O.  -DKLOCAL_FALSE selects the other expansion.
 #include <cstdio>
 #include <cstdlib>
 #include <string>
@@ -29,7 +29,11 @@ constexpr int kComponents = Riemann::kComponents;
 #include "mini/integrator/lobatto.hpp"
 using Gx = mini::integrator::Lobatto<Scalar, kDegrees + 1>;
 #include "mini/polynomial/hexahedron.hpp"
+#ifdef KLOCAL_FALSE
 using Projection = mini::polynomial::Hexahedron<Gx, Gx, Gx, kComponents, false>;
+#else   // demo/laminar/shockless.hpp:66-69: FR uses the kLocal == true expansion (coefficients = det(J) u)
+using Projection = mini::polynomial::Hexahedron<Gx, Gx, Gx, kComponents, true>;
+#endif
 #include "mini/mesh/part.hpp"
 using Part = mini::mesh::part::Part<int64_t, Projection>;
 using Global = typename Part::Global;

@@ -76,8 +76,6 @@ struct Legendre {  // integrator/legendre.hpp:20-80; the rule itself lives in th
 namespace polynomial {
 template <class Gx, class Gy, class Gz, int kComponents, bool kL = false>
 struct Hexahedron {  // polynomial/hexahedron.hpp:41-65
-  static_assert(!kL, "libminicfd_b200 implements the kLocal == false expansion only (coefficients = nodal values of u); "
-                     "Hexahedron<..., true> stores det(J) u and changes gradients, Hessians and the residual scaling");
   static_assert(Gx::Q == Gy::Q && Gy::Q == Gz::Q, "the B200 path needs the same rule in all directions");
   static_assert(Gx::Q == 3 || Gx::Q == 4, "degree 2 or 3");
   using Scalar = typename Gx::Scalar;
@@ -407,6 +405,7 @@ class FiniteElementB200 : public temporal::System<typename P::Scalar> {
 
   explicit FiniteElementB200(Part *part_ptr, int device = -1, double c_next = 0.0) : part_ptr_(part_ptr) {
     mcfd_config cfg{kScheme, Part::kDegrees, Riemann::kKind, device, c_next, Riemann::kDiffusion, 0};
+    if constexpr (requires { Part::Polynomial::kLocal; }) cfg.k_local = Part::Polynomial::kLocal ? 1 : 0;
     if (mcfd_create(&cfg, &ctx_) != 0) throw std::runtime_error(std::string("mcfd_create: ") + mcfd_last_error(nullptr));
     auto &p = *part_ptr_;
     b200::Check(mcfd_set_mesh(ctx_, (int64_t)p.nodes_.size() / 3, p.nodes_.data(), p.n_local_, p.n_ghost_,
@@ -449,10 +448,16 @@ class FiniteElementB200 : public temporal::System<typename P::Scalar> {
     } else {
       Column column(part().GetCellDataSize());
       constexpr int N = Part::Polynomial::N, K = Part::kComponents;
+      std::vector<double> det;
+      if constexpr (Part::Polynomial::kLocal) {   // Hexahedron::SetValue: coeff = value * det J (hexahedron.hpp:344-349)
+        det.resize((size_t)part().CountLocalCells() * N);
+        b200::Check(mcfd_get_jacobian_determinants(ctx_, det.data()), ctx_, "mcfd_get_jacobian_determinants");
+      }
       for (typename Part::Index c = 0; c < part().CountLocalCells(); ++c) {
         for (int q = 0; q < N; ++q) {
           Value v = func(part().NodeCoordinate(c, q));
-          for (int k = 0; k < K; ++k) column[(c * N + q) * K + k] = v[k];
+          const double scale = det.empty() ? 1.0 : det[(size_t)c * N + q];
+          for (int k = 0; k < K; ++k) column[(c * N + q) * K + k] = v[k] * scale;
         }
       }
       SetSolutionColumn(column);

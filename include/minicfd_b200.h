@@ -84,7 +84,12 @@ typedef struct {
   int32_t device;    /* CUDA device ordinal, -1 = current device */
   double fr_c_next;  /* MCFD_FR_GENERAL only: the `c_next` of fr::General(part, c_next), fr/general.hpp:218-219 */
   int32_t diffusion; /* mcfd_diffusion; the viscous path exists for MCFD_FR_LOBATTO */
-  int32_t reserved;  /* 0 */
+  int32_t k_local;   /* 0 | 1: the kLocal flag of mini::polynomial::Hexahedron<Gx, Gy, Gz, K, kLocal>
+                      * (include/mini/polynomial/hexahedron.hpp:41-56, 338-343).  With 1 a column holds det(J) u
+                      * instead of u — the reference's laminar drivers use that for FR
+                      * (demo/laminar/shockless.hpp:62-69) — gradients and Hessians are those of that interpolant
+                      * (hexahedron.hpp:397-408, 526-562) and residual columns are d(det u)/dt (fr/general.hpp:251-253).
+                      * FR schemes, Euler and Navier-Stokes; on the device and in the halo buffers the state stays u. */
 } mcfd_config;
 
 /* -- life cycle ------------------------------------------------------------------------------ */
@@ -200,6 +205,9 @@ int mcfd_update_cell_viscosity(mcfd_ctx *ctx, double time_scale);
 /* Gauss-Legendre points of the local cells, [n_local][Q^3][3], in the order of integrator::Hexahedron
  * (include/mini/integrator/hexahedron.hpp:66-80): where FiniteElement::Approximate samples its function. */
 int mcfd_get_quadrature_points(const mcfd_ctx *ctx, double *xyz);
+/* det J at the nodes of the local cells, [n_local][N] (integrator/hexahedron.hpp GetJacobianDeterminant): what a
+ * k_local host multiplies nodal values by to obtain column entries (Hexahedron::SetValue, hexahedron.hpp:344-349). */
+int mcfd_get_jacobian_determinants(const mcfd_ctx *ctx, double *det);
 /* Replaces Cell::Approximate -> Projection::Approximate (include/mini/polynomial/projection.hpp:28-43, 170-173): the L2
  * projection of a function given by its values at those points, values [n_local][Q^3][5], becomes the solution.
  * For MCFD_DG_GENERAL mcfd_get_boundary_points returns the faces' Gauss points, [face][Q*Q][3]. */

@@ -21,7 +21,7 @@ TIME_CALLBACK = C.CFUNCTYPE(None, C.c_void_p, C.c_double)
 
 class Config(C.Structure):
     _fields_ = [("scheme", C.c_int32), ("degree", C.c_int32), ("riemann", C.c_int32), ("device", C.c_int32),
-                ("fr_c_next", C.c_double), ("diffusion", C.c_int32), ("reserved", C.c_int32)]
+                ("fr_c_next", C.c_double), ("diffusion", C.c_int32), ("k_local", C.c_int32)]
 
 
 class McfdError(RuntimeError):
@@ -60,6 +60,7 @@ SYMBOLS = {
     "mcfd_get_damping_matrices": (C.c_int, [_P, _D]),
     "mcfd_update_cell_viscosity": (C.c_int, [_P, C.c_double]),
     "mcfd_get_quadrature_points": (C.c_int, [_P, _D]),
+    "mcfd_get_jacobian_determinants": (C.c_int, [_P, _D]),
     "mcfd_project": (C.c_int, [_P, _D]),
     "mcfd_set_time_callback": (C.c_int, [_P, TIME_CALLBACK, _P]),
     "mcfd_count_local_cells": (C.c_int64, [_P]),
@@ -131,10 +132,11 @@ def time_step_static(scheme, degree, n_cells, column_ptr, length_ptr, dt_guess, 
 class Context:
     """One mcfd_ctx: a part of the mesh resident on one GPU."""
 
-    def __init__(self, scheme=FR_LOBATTO, degree=2, riemann=HLLC, device=-1, fr_c_next=0.0, diffusion=INVISCID):
+    def __init__(self, scheme=FR_LOBATTO, degree=2, riemann=HLLC, device=-1, fr_c_next=0.0, diffusion=INVISCID,
+                 k_local=False):
         self.lib = load()
         self.h = _P()
-        cfg = Config(scheme, degree, riemann, device, fr_c_next, diffusion, 0)
+        cfg = Config(scheme, degree, riemann, device, fr_c_next, diffusion, 1 if k_local else 0)
         rc = self.lib.mcfd_create(C.byref(cfg), C.byref(self.h))
         if rc != 0:
             raise McfdError(f"mcfd_create failed ({rc}): {self.lib.mcfd_last_error(None).decode()}")
@@ -177,6 +179,11 @@ class Context:
     def cell_viscosity(self, n_cells=None):
         out = np.empty((self.n_local if n_cells is None else n_cells, 5))
         self._check(self.lib.mcfd_get_cell_viscosity(self.h, _dp(out)))
+        return out
+
+    def jacobian_determinants(self):
+        out = np.empty((self.n_local, self.q ** 3))
+        self._check(self.lib.mcfd_get_jacobian_determinants(self.h, _dp(out)))
         return out
 
     def quadrature_points(self):

@@ -246,7 +246,13 @@ MCFD_HD int FaceOf(int d, bool plus) {  // local face id of the -/+ side in dire
 // Contracting with n first:  w = inv^T n,  v_a = w^T dJ_a,  m_a(b) = -sum_s v_a(s) inv(s, b),
 //     t(a) = sum_b Hl(a, b) w(b) + sum_b gl(b) m_a(b),     (H n)(i) = sum_a inv(i, a) t(a).
 // dJ_a of the trilinear map has three distinct rows: A = d2x/dxi deta, B = d2x/dzeta dxi, C = d2x/deta dzeta.
-template <int Q>
+// kLocal == true (polynomial/hexahedron.hpp:171-219, 397-408, 526-562): `u` holds U = det(J) u, the interpolated
+// quantity; with dg = grad_xi det, dh = Hessian_xi det (coordinate/cell.hpp:157-199) the same contraction gives
+//   grad u = inv (gl - dg u) / det,
+//   t(a)  = [sum_b Hl(a,b) w_b]/det + sum_b gl_b (m_a(b)/det - w_b dg_a/det^2) - (dg.w)/det^2 gl_a
+//           - [(sum_b dh(a,b) w_b + sum_b dg_b m_a(b))/det^2 - 2 dg_a (dg.w)/det^3] U,        (H n)(i) = sum_a inv(i,a) t(a)
+// so that the outputs are again the gradient and Hessian.normal of u and the stage kernel does not change.
+template <int Q, bool kLocal = false>
 MCFD_HD void TraceCellNode(int n, const double *u, int us, const double *geo, int gs, double *grad,
     double *hn, int os) {
   constexpr int FQ = Q * Q;
@@ -275,11 +281,65 @@ MCFD_HD void TraceCellNode(int n, const double *u, int us, const double *geo, in
 #pragma unroll
     for (int d = 0; d < 3; ++d) inv[k][d] = m.s[d][k] * inv_det;
   }
+  double A[3], B[3], C[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const double c4 = geo[(9 + k) * gs], c5 = geo[(12 + k) * gs], c6 = geo[(15 + k) * gs], c7 = geo[(18 + k) * gs];
+    A[k] = fma(z, c7, c4);
+    B[k] = fma(e, c7, c6);
+    C[k] = fma(x, c7, c5);
+  }
+  double dg[3] = {0, 0, 0}, dh[3][3], big_u[5];
+  if (kLocal) {
+    // P_a = inv dJ_a (xyz x xyz); dJ_0 has rows (0, A, B), dJ_1 (A, 0, C), dJ_2 (B, C, 0)
+    double Pm[3][3][3], tr[3];
+#pragma unroll
+    for (int xx = 0; xx < 3; ++xx) {
+#pragma unroll
+      for (int y = 0; y < 3; ++y) {
+        Pm[0][xx][y] = inv[xx][1] * A[y] + inv[xx][2] * B[y];
+        Pm[1][xx][y] = inv[xx][0] * A[y] + inv[xx][2] * C[y];
+        Pm[2][xx][y] = inv[xx][0] * B[y] + inv[xx][1] * C[y];
+      }
+    }
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      tr[a] = Pm[a][0][0] + Pm[a][1][1] + Pm[a][2][2];
+      dg[a] = m.det * tr[a];
+    }
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+#pragma unroll
+      for (int b = 0; b < 3; ++b) {
+        double t2 = 0, tpp = 0;
+        if (a != b) {
+          const int p3 = 3 - a - b;
+#pragma unroll
+          for (int xx = 0; xx < 3; ++xx) t2 += inv[xx][p3] * geo[(18 + xx) * gs];
+        }
+#pragma unroll
+        for (int xx = 0; xx < 3; ++xx) {
+#pragma unroll
+          for (int y = 0; y < 3; ++y) tpp += Pm[a][xx][y] * Pm[b][y][xx];
+        }
+        dh[a][b] = (t2 + tr[a] * tr[b] - tpp) * m.det;
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < 5; ++c) big_u[c] = u[(size_t)(n * 5 + c) * us];
+  }
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
 #pragma unroll
-    for (int c = 0; c < 5; ++c)
-      grad[(size_t)(n * 15 + k * 5 + c) * os] = inv[k][0] * gl[0][c] + inv[k][1] * gl[1][c] + inv[k][2] * gl[2][c];
+    for (int c = 0; c < 5; ++c) {
+      if (kLocal) {
+        const double uc = big_u[c] * inv_det;
+        grad[(size_t)(n * 15 + k * 5 + c) * os] = (inv[k][0] * (gl[0][c] - dg[0] * uc) + inv[k][1] * (gl[1][c] - dg[1] * uc)
+            + inv[k][2] * (gl[2][c] - dg[2] * uc)) * inv_det;
+      } else {
+        grad[(size_t)(n * 15 + k * 5 + c) * os] = inv[k][0] * gl[0][c] + inv[k][1] * gl[1][c] + inv[k][2] * gl[2][c];
+      }
+    }
   }
   if (idx[0] != 0 && idx[0] != Q - 1 && idx[1] != 0 && idx[1] != Q - 1 && idx[2] != 0 && idx[2] != Q - 1) return;
   // local Hessian XX XY XZ YY YZ ZZ (hexahedron.hpp:155-170, 439-447)
@@ -318,14 +378,6 @@ MCFD_HD void TraceCellNode(int n, const double *u, int us, const double *geo, in
       }
     }
   }
-  double A[3], B[3], C[3];
-#pragma unroll
-  for (int k = 0; k < 3; ++k) {
-    const double c4 = geo[(9 + k) * gs], c5 = geo[(12 + k) * gs], c6 = geo[(15 + k) * gs], c7 = geo[(18 + k) * gs];
-    A[k] = fma(z, c7, c4);
-    B[k] = fma(e, c7, c6);
-    C[k] = fma(x, c7, c5);
-  }
 #pragma unroll
   for (int d = 0; d < 3; ++d) {
     if (idx[d] != 0 && idx[d] != Q - 1) continue;
@@ -348,6 +400,15 @@ MCFD_HD void TraceCellNode(int n, const double *u, int us, const double *geo, in
 #pragma unroll
       for (int b = 0; b < 3; ++b) mm[a][b] = -(v[a][0] * inv[0][b] + v[a][1] * inv[1][b] + v[a][2] * inv[2][b]);
     }
+    double dgw = 0, mbu[3] = {0, 0, 0};
+    if (kLocal) {
+      dgw = dg[0] * w[0] + dg[1] * w[1] + dg[2] * w[2];
+      const double id2 = inv_det * inv_det;
+#pragma unroll
+      for (int a = 0; a < 3; ++a)
+        mbu[a] = ((dh[a][0] * w[0] + dh[a][1] * w[1] + dh[a][2] * w[2]) + (dg[0] * mm[a][0] + dg[1] * mm[a][1] + dg[2] * mm[a][2])) * id2
+               - 2 * dg[a] * dgw * id2 * inv_det;
+    }
 #pragma unroll
     for (int c = 0; c < 5; ++c) {
       double t[3];
@@ -356,6 +417,13 @@ MCFD_HD void TraceCellNode(int n, const double *u, int us, const double *geo, in
       t[2] = hl[2][c] * w[0] + hl[4][c] * w[1] + hl[5][c] * w[2];
 #pragma unroll
       for (int a = 0; a < 3; ++a) t[a] += gl[0][c] * mm[a][0] + gl[1][c] * mm[a][1] + gl[2][c] * mm[a][2];
+      if (kLocal) {
+        const double glw = gl[0][c] * w[0] + gl[1][c] * w[1] + gl[2][c] * w[2];
+        const double id2 = inv_det * inv_det;
+#pragma unroll
+        for (int a = 0; a < 3; ++a)
+          t[a] = t[a] * inv_det - glw * dg[a] * id2 - dgw * id2 * gl[a][c] - mbu[a] * big_u[c];
+      }
 #pragma unroll
       for (int k = 0; k < 3; ++k)
         hn[(size_t)(pt * 15 + k * 5 + c) * os] = inv[k][0] * t[0] + inv[k][1] * t[1] + inv[k][2] * t[2];
@@ -1761,7 +1829,7 @@ struct TraceShape {
   static constexpr size_t kSharedBytes = (size_t)(F + kGeomRows) * kTile * sizeof(double);
 };
 #ifdef __CUDACC__
-template <int Q>
+template <int Q, bool kLocal = false>
 __global__ void __launch_bounds__(TraceShape<Q>::NW * 32, MCFD_TRACE_MINB) TraceKernel(const double *u,
     const double *geom, double *grad, double *hn, int tile_begin, int cell_begin, int cell_end) {
   using S = TraceShape<Q>;
@@ -1784,21 +1852,66 @@ __global__ void __launch_bounds__(TraceShape<Q>::NW * 32, MCFD_TRACE_MINB) Trace
     for (int i = threadIdx.x; i < kGeomRows * kTile; i += T) sG[i] = geom[(size_t)tile * kGeomRows * kTile + i];
   }
   __syncthreads();
+  if (kLocal) {   // the interpolated quantity is U = det(J) u (the state holds u): scale the staged tile
+    for (int n = warp; n < S::N; n += S::NW) {
+      const Metric mt = ComputeMetric(sG + lane, kTile, c_tab.xi[n / (Q * Q)], c_tab.xi[(n / Q) % Q], c_tab.xi[n % Q]);
+#pragma unroll
+      for (int c = 0; c < 5; ++c) sU[(n * 5 + c) * kTile + lane] *= mt.det;
+    }
+    __syncthreads();
+  }
   const int cell = tile * kTile + lane;
   if (cell < cell_begin || cell >= cell_end) return;
   double *gdst = grad + (size_t)tile * S::N * 15 * kTile + lane;
   double *hdst = hn + (size_t)tile * 6 * Q * Q * 15 * kTile + lane;
-  for (int n = warp; n < S::N; n += S::NW) TraceCellNode<Q>(n, sU + lane, kTile, sG + lane, kTile, gdst, hdst, kTile);
+  for (int n = warp; n < S::N; n += S::NW)
+    TraceCellNode<Q, kLocal>(n, sU + lane, kTile, sG + lane, kTile, gdst, hdst, kTile);
+}
+// kLocal == true contexts keep u on the device; columns hold U = det(J) u (polynomial/hexahedron.hpp:338-343).
+// In-place conversion of a tile range (invert: U -> u) or of a column [cell][node][comp] (u -> U, or residuals).
+template <int Q>
+__global__ void ScaleTilesKernel(double *tiles, const double *geom, int cell_begin, int cell_end, int invert) {
+  constexpr int N = Q * Q * Q, F = 5 * N;
+  const int cell = cell_begin + blockIdx.x * blockDim.x + threadIdx.x;
+  if (cell >= cell_end) return;
+  const int tile = cell >> 5, tl = cell & 31;
+  for (int n = 0; n < N; ++n) {
+    const Metric mt = ComputeMetric(geom + (size_t)tile * kGeomRows * kTile + tl, kTile, c_tab.xi[n / (Q * Q)],
+        c_tab.xi[(n / Q) % Q], c_tab.xi[n % Q]);
+    const double s = invert ? 1.0 / mt.det : mt.det;
+    for (int c = 0; c < 5; ++c) tiles[((size_t)tile * F + n * 5 + c) * kTile + tl] *= s;
+  }
+}
+template <int Q>
+__global__ void ScaleColumnKernel(double *column, const double *geom, int n_cells) {
+  constexpr int N = Q * Q * Q;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;     // (cell, node)
+  if (i >= n_cells * N) return;
+  const int cell = i / N, n = i % N;
+  const Metric mt = ComputeMetric(geom + (size_t)(cell >> 5) * kGeomRows * kTile + (cell & 31), kTile, c_tab.xi[n / (Q * Q)],
+      c_tab.xi[(n / Q) % Q], c_tab.xi[n % Q]);
+  for (int c = 0; c < 5; ++c) column[(size_t)i * 5 + c] *= mt.det;
 }
 #else
-template <int Q>
+template <int Q, bool kLocal = false>
 void RunTraceOnHost(const double *u, const double *geom, double *grad, double *hn, int n_cells) {
   constexpr int N = Q * Q * Q, F = 5 * N;
+  static double big[F];   // U = det u of the current cell when kLocal
   for (int cell = 0; cell < n_cells; ++cell) {
     const int tile = cell >> 5, lane = cell & 31;
+    const double *src = u + (size_t)tile * F * kTile + lane;
+    const double *geo = geom + (size_t)tile * kGeomRows * kTile + lane;
+    int us = kTile;
+    if (kLocal) {
+      for (int n = 0; n < N; ++n) {
+        const Metric mt = ComputeMetric(geo, kTile, c_tab.xi[n / (Q * Q)], c_tab.xi[(n / Q) % Q], c_tab.xi[n % Q]);
+        for (int c = 0; c < 5; ++c) big[n * 5 + c] = src[(size_t)(n * 5 + c) * kTile] * mt.det;
+      }
+      src = big; us = 1;
+    }
     for (int n = 0; n < N; ++n)
-      TraceCellNode<Q>(n, u + (size_t)tile * F * kTile + lane, kTile, geom + (size_t)tile * kGeomRows * kTile + lane,
-          kTile, grad + (size_t)tile * N * 15 * kTile + lane, hn + (size_t)tile * 6 * Q * Q * 15 * kTile + lane, kTile);
+      TraceCellNode<Q, kLocal>(n, src, us, geo, kTile, grad + (size_t)tile * N * 15 * kTile + lane,
+          hn + (size_t)tile * 6 * Q * Q * 15 * kTile + lane, kTile);
   }
 }
 #endif

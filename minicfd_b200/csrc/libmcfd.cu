@@ -179,8 +179,23 @@ int LaunchTrace(mcfd_ctx *ctx, const double *u, int64_t cell_begin, int64_t cell
   cudaError_t e = EnsureTables(ctx);
   if (e != cudaSuccess) return Fail(ctx, MCFD_ERR_CUDA, cudaGetErrorString(e));
   if (ctx->q == 3) {
+    if (ctx->cfg.k_local)
+      TraceKernel<3, true><<<tile_end - tile_begin, TraceShape<3>::NW * 32, TraceShape<3>::kSharedBytes, ctx->stream>>>(u,
+          ctx->geom.p, ctx->grad.p, ctx->hn.p, tile_begin, (int)cell_begin, (int)cell_end);
+    else
     TraceKernel<3><<<tile_end - tile_begin, TraceShape<3>::NW * 32, TraceShape<3>::kSharedBytes, ctx->stream>>>(u, ctx->geom.p,
         ctx->grad.p, ctx->hn.p, tile_begin, (int)cell_begin, (int)cell_end);
+    e = cudaGetLastError();
+  } else if (ctx->cfg.k_local) {
+    auto kernel = TraceKernel<4, true>;
+    static bool configured = false;
+    if (!configured) {
+      e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TraceShape<4>::kSharedBytes);
+      if (e != cudaSuccess) return Fail(ctx, MCFD_ERR_CUDA, cudaGetErrorString(e));
+      configured = true;
+    }
+    kernel<<<tile_end - tile_begin, TraceShape<4>::NW * 32, TraceShape<4>::kSharedBytes, ctx->stream>>>(u, ctx->geom.p, ctx->grad.p,
+        ctx->hn.p, tile_begin, (int)cell_begin, (int)cell_end);
     e = cudaGetLastError();
   } else {
     auto kernel = TraceKernel<4>;
@@ -304,6 +319,28 @@ int LaunchConvert(mcfd_ctx *ctx, double *tiles, double *column, const int *cells
   return MCFD_OK;
 }
 
+// kLocal == true contexts: columns hold U = det(J) u, the device keeps u
+int ScaleColumnByDet(mcfd_ctx *ctx, double *column_dev) {
+  if (!ctx->cfg.k_local) return MCFD_OK;
+  MCFD_CUDA(ctx, EnsureTables(ctx));
+  const int nl = (int)ctx->mesh.n_local, n = nl * ctx->n_nodes;
+  if (ctx->q == 3) ScaleColumnKernel<3><<<(n + 255) / 256, 256, 0, ctx->stream>>>(column_dev, ctx->geom.p, nl);
+  else ScaleColumnKernel<4><<<(n + 255) / 256, 256, 0, ctx->stream>>>(column_dev, ctx->geom.p, nl);
+  MCFD_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  return MCFD_OK;
+}
+int UnscaleTilesByDet(mcfd_ctx *ctx, double *tiles) {
+  if (!ctx->cfg.k_local) return MCFD_OK;
+  MCFD_CUDA(ctx, EnsureTables(ctx));
+  const int nl = (int)ctx->mesh.n_local;
+  if (ctx->q == 3) ScaleTilesKernel<3><<<(nl + 127) / 128, 128, 0, ctx->stream>>>(tiles, ctx->geom.p, 0, nl, 1);
+  else ScaleTilesKernel<4><<<(nl + 127) / 128, 128, 0, ctx->stream>>>(tiles, ctx->geom.p, 0, nl, 1);
+  MCFD_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  return MCFD_OK;
+}
+
 int RequireMesh(mcfd_ctx *ctx) {
   if (!ctx) return MCFD_ERR_ARG;
   if (!ctx->has_mesh) return Fail(ctx, MCFD_ERR_STATE, "mcfd_set_mesh has not been called");
@@ -360,6 +397,10 @@ int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
   // type, built here for Navier-Stokes
   if (config->diffusion != MCFD_INVISCID && config->scheme == MCFD_DG_LOBATTO)
     return Fail(nullptr, MCFD_ERR_ARG, "the reference's DG schemes have no diffusive terms; use MCFD_FR_LOBATTO or MCFD_FR_GENERAL");
+  if (config->k_local != 0 && config->k_local != 1) return Fail(nullptr, MCFD_ERR_ARG, "k_local must be 0 or 1");
+  if (config->k_local && (config->scheme == MCFD_DG_LOBATTO || config->scheme == MCFD_DG_GENERAL ||
+                          config->diffusion == MCFD_CELL_VISCOSITY_DDG))
+    return Fail(nullptr, MCFD_ERR_ARG, "k_local is built for the FR schemes on Euler and Navier-Stokes");
   if (config->diffusion == MCFD_CELL_VISCOSITY_DDG && config->scheme != MCFD_FR_LOBATTO)
     return Fail(nullptr, MCFD_ERR_ARG, "MCFD_CELL_VISCOSITY_DDG is built for MCFD_FR_LOBATTO only");
   int n_dev = 0;
@@ -715,6 +756,19 @@ int mcfd_set_cell_viscosity(mcfd_ctx *ctx, int64_t n_cells, const double *nu) {
   return MCFD_OK;
 }
 
+int mcfd_get_jacobian_determinants(const mcfd_ctx *ctx, double *det) {
+  if (!ctx || !ctx->has_mesh || !det) return MCFD_ERR_STATE;
+  const int q = ctx->q;
+  for (int64_t c = 0; c < ctx->mesh.n_local; ++c) {
+    const double *g = &ctx->mesh.coef[c * kGeomRows];
+    for (int i = 0; i < q; ++i) for (int j = 0; j < q; ++j) for (int k = 0; k < q; ++k) {
+      const HostMetric m = ComputeMetricHost(g, ctx->tables.xi[i], ctx->tables.xi[j], ctx->tables.xi[k]);
+      *det++ = m.det;
+    }
+  }
+  return MCFD_OK;
+}
+
 int mcfd_get_quadrature_points(const mcfd_ctx *ctx, double *xyz) {
   if (!ctx || !ctx->has_mesh || !xyz) return MCFD_ERR_STATE;
   if (ctx->cfg.scheme != MCFD_DG_GENERAL) return MCFD_ERR_STATE;
@@ -759,13 +813,15 @@ int64_t mcfd_cell_data_size(const mcfd_ctx *ctx) {
 int mcfd_set_solution_device(mcfd_ctx *ctx, const double *column_dev) {
   if (int s = RequireMesh(ctx)) return s;
   if (ctx->rk_order) return Fail(ctx, MCFD_ERR_STATE, "an RK step is open");
-  return LaunchConvert<true>(ctx, ctx->u[ctx->cur].p, const_cast<double *>(column_dev), nullptr,
-      ctx->mesh.n_local);
+  if (int s = LaunchConvert<true>(ctx, ctx->u[ctx->cur].p, const_cast<double *>(column_dev), nullptr, ctx->mesh.n_local))
+    return s;
+  return UnscaleTilesByDet(ctx, ctx->u[ctx->cur].p);
 }
 
 int mcfd_get_solution_device(mcfd_ctx *ctx, double *column_dev) {
   if (int s = RequireMesh(ctx)) return s;
-  return LaunchConvert<false>(ctx, ctx->u[ctx->cur].p, column_dev, nullptr, ctx->mesh.n_local);
+  if (int s = LaunchConvert<false>(ctx, ctx->u[ctx->cur].p, column_dev, nullptr, ctx->mesh.n_local)) return s;
+  return ScaleColumnByDet(ctx, column_dev);
 }
 
 int mcfd_set_solution(mcfd_ctx *ctx, const double *column) {
@@ -804,12 +860,14 @@ int mcfd_residual(mcfd_ctx *ctx, double t, double *column, double *column_dev) {
     if (int s = LaunchDgmTaylor(ctx, u, 0, ctx->n_cells)) return s;
   }
   if (int s = LaunchStage(ctx, u, u, ctx->res.p, kModeResidual, 0.0, 0, ctx->total_blocks)) return s;
-  if (column_dev) {
+  if (column_dev) {   // kLocal: the column is dU/dt = det du/dt (fr/general.hpp:251-253)
     if (int s = LaunchConvert<false>(ctx, ctx->res.p, column_dev, nullptr, ctx->mesh.n_local)) return s;
+    if (int s = ScaleColumnByDet(ctx, column_dev)) return s;
   }
   if (column) {
     if (int s = EnsureColumn(ctx)) return s;
     if (int s = LaunchConvert<false>(ctx, ctx->res.p, ctx->column.p, nullptr, ctx->mesh.n_local)) return s;
+    if (int s = ScaleColumnByDet(ctx, ctx->column.p)) return s;
     size_t bytes = (size_t)ctx->mesh.n_local * ctx->fields * sizeof(double);
     MCFD_CUDA(ctx, cudaMemcpyAsync(column, ctx->column.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
   }
@@ -962,6 +1020,7 @@ int mcfd_rk_step_device(mcfd_ctx *ctx, int order, double t, const double *dt_dev
 int mcfd_limiter_reconstruct(mcfd_ctx *ctx, int kind) {
   if (int s = RequireMesh(ctx)) return s;
   if (kind != 0 && kind != 1) return Fail(ctx, MCFD_ERR_ARG, "limiter kind must be 0 (average) or 1 (majority)");
+  if (ctx->cfg.k_local) return Fail(ctx, MCFD_ERR_STATE, "the limiters are built for kLocal == false");
   if (ctx->cfg.scheme == MCFD_DG_GENERAL) return Fail(ctx, MCFD_ERR_STATE, "the limiters are built for the nodal expansions");
   if (ctx->rk_order) return Fail(ctx, MCFD_ERR_STATE, "an RK step is open");
   int n = (int)ctx->mesh.n_local, threads = 128, blocks = (n + threads - 1) / threads;
@@ -1087,6 +1146,7 @@ int mcfd_eigen_matrices(mcfd_ctx *ctx, int64_t n, const double *conservative, co
 
 static int LimiterWeno(mcfd_ctx *ctx, double w0, double eps, int phase, bool eigen) {
   if (int s = RequireMesh(ctx)) return s;
+  if (ctx->cfg.k_local) return Fail(ctx, MCFD_ERR_STATE, "the limiters are built for kLocal == false");
   if (ctx->cfg.scheme == MCFD_DG_GENERAL) {
     if (eigen) return Fail(ctx, MCFD_ERR_STATE, "weno::Eigen is built for the nodal expansions");
     if (phase < -1 || phase > 1) return Fail(ctx, MCFD_ERR_ARG, "phase must be -1 (both), 0 (inner cells) or 1 (inter cells)");

@@ -226,6 +226,19 @@ inline Tables BuildTables(int degree, int scheme, int n_warps, int sub, double c
   return t;
 }
 
+// det J at local coordinates (x, e, z) from one cell's 21 coefficients (host copy of ComputeMetric's determinant)
+struct HostMetric { double det; };
+inline HostMetric ComputeMetricHost(const double *g, double x, double e, double z) {
+  double r[3][3];
+  for (int d = 0; d < 3; ++d) {
+    r[0][d] = g[0 + d] + g[9 + d] * e + g[15 + d] * z + g[18 + d] * e * z;
+    r[1][d] = g[3 + d] + g[9 + d] * x + g[12 + d] * z + g[18 + d] * x * z;
+    r[2][d] = g[6 + d] + g[12 + d] * e + g[15 + d] * x + g[18 + d] * x * e;
+  }
+  return HostMetric{r[0][0] * (r[1][1] * r[2][2] - r[1][2] * r[2][1]) - r[0][1] * (r[1][0] * r[2][2] - r[1][2] * r[2][0])
+                    + r[0][2] * (r[1][0] * r[2][1] - r[1][1] * r[2][0])};
+}
+
 // ------------------------------------------------------------------------------------------------
 // Connectivity of one part.
 // ------------------------------------------------------------------------------------------------

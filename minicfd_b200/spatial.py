@@ -15,11 +15,12 @@ from .part import Part, cell_points
 
 class Spatial:
     def __init__(self, part: Part, *, scheme=capi.FR_LOBATTO, degree=2, riemann=capi.HLLC, device=-1,
-                 comm=None, fr_c_next=0.0, diffusion=capi.INVISCID):
+                 comm=None, fr_c_next=0.0, diffusion=capi.INVISCID, k_local=False):
         self.part = part
         self.degree = degree
         self.scheme = scheme
-        self.ctx = capi.Context(scheme, degree, riemann, device, fr_c_next, diffusion)
+        self.k_local = bool(k_local)
+        self.ctx = capi.Context(scheme, degree, riemann, device, fr_c_next, diffusion, k_local)
         self.kfields = self.ctx.kfields
         m = part.mesh
         self.ctx.set_mesh(m.nodes, part.cell_nodes, part.n_local, part.n_ghost, part.bfaces, part.btags,
@@ -54,6 +55,8 @@ class Spatial:
             return
         pts = cell_points(self.part.mesh.nodes, self.part.cell_nodes[:self.part.n_local], self.degree)
         vals = np.asarray(func(pts))
+        if self.k_local:   # Hexahedron::SetValue with kLocal == true: coeff = value * det J (hexahedron.hpp:344-349)
+            vals = vals * self.ctx.jacobian_determinants()[:, :, None]
         self.SetSolutionColumn(vals.reshape(-1))
 
     def _set_bc(self, tag, kind, func=None, time_dependent=True):

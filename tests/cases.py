@@ -159,3 +159,8 @@ ENERGY_AMP = 5e-2          # noise level at which some, not all, (cell, componen
 # ---- dg::General on the modal Projection polynomial with Gauss-Legendre rules ------------------
 DGM_GOLDEN_CASES = [("dgm_p2_hllc", 2, 1), ("dgm_p2_exact", 2, 0), ("dgm_p3_ausm", 3, 2)]
 DGM_WENO_GOLDEN_CASES = [("dgm_weno_p2_hllc", 2, 1), ("dgm_weno_p3_hllc", 3, 1)]   # DGFEM + LIMITER of the reference
+
+
+# ---- kLocal == true expansions: columns hold det(J) u (demo/laminar/shockless.hpp:66-69; BASELINE config 4) -------
+LOCAL_GOLDEN_CASES = [("local_euler_p2_hllc", 2, 1, False), ("local_ns_p2_hllc", 2, 1, True),
+                      ("local_ns_p3_exact", 3, 0, True)]    # (name, degree, riemann, viscous)

@@ -70,7 +70,8 @@ def stage(mesh, degree, scheme, riemann, column_in, *, n_local=None, n_ghost=0, 
                          C.c_int64(0 if pairs is None else len(pairs)), _ip(pairs), _i32(kinds), _dp(bv),
                          _dp(column_in), _dp(u0), C.c_int(mode), C.c_double(dt), _dp(out), err, C.c_int(256),
                          C.c_double(c_next),
-                         None if viscous is None else _dp(np.ascontiguousarray(viscous, dtype=np.float64)),
+                         None if viscous is None else _dp(np.ascontiguousarray(
+                             (list(viscous) + [0.0])[:5], dtype=np.float64)),
                          None if cell_nu is None else _dp(np.ascontiguousarray(cell_nu, dtype=np.float64)))
     if rc != 0:
         raise RuntimeError(err.value.decode())

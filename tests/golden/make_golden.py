@@ -100,6 +100,24 @@ def main():
         np.savez_compressed(os.path.join(HERE, name + ".npz"), u=u, limited=limited, u_rk3=r.get_solution(),
                             nodes=m.nodes, cells=m.cells, bfaces=m.bfaces, btags=m.btags)
         print(name, np.abs(limited - u).max())
+    # fr::Lobatto on Hexahedron<..., true>: columns are det(J) u; Euler and Navier-Stokes + direct DG
+    for name, degree, riemann, viscous in cases.LOCAL_GOLDEN_CASES:
+        r = refapi.Ref(m, degree=degree, scheme=refapi.FR_LOCAL_VISCOUS if viscous else refapi.FR_LOCAL, riemann=riemann)
+        if viscous:
+            cases.apply_viscous_ref(r)
+        else:
+            cases.apply_bcs_ref(r)
+        r.approximate(refapi.F_CONST, [1, 1, 1, 1, 1])          # SetValue(1): the column is det J
+        det = r.get_solution().reshape(m.n_cells, -1, 5)[:, :, 0]
+        u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), amp=1e-4).reshape(m.n_cells, -1, 5)
+        column = (u * det[:, :, None]).reshape(-1)
+        r.set_solution(column)
+        res = r.residual(cases.GOLDEN_T)
+        dt = r.time_step(1.0, 3)
+        r.rk_update(3, 0.0, cases.GOLDEN_DT, 1)
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), det=det, u=column, residual=res, dt=dt,
+                            u_rk3=r.get_solution(), nodes=m.nodes, cells=m.cells, bfaces=m.bfaces, btags=m.btags)
+        print(name, np.linalg.norm(res), dt)
     # WithLimiter<fr::Lobatto, weno::Lazy>: the limiter's action on a column, and an RK3 step with it
     for name, degree, riemann in cases.WENO_GOLDEN_CASES:
         r = refapi.Ref(m, degree=degree, scheme=refapi.FR_WENO_LAZY, riemann=riemann, weno=cases.WENO)

@@ -55,7 +55,7 @@ int emu_stage(int degree, int scheme, int riemann, int64_t n_nodes, const double
     const int64_t *bface_nodes, const int32_t *bface_tags, int64_t n_pairs, const int64_t *pairs,
     const int32_t *tag_kinds, const double *bvals, const double *column_in, const double *column_u0,
     int mode, double dt, double *column_out, char *err, int err_len, double c_next,
-    const double *viscous /* null, or beta0, beta1, nu, prandtl */,
+    const double *viscous /* null, or beta0, beta1, nu, prandtl, kLocal (0 / 1: the traces interpolate det u) */,
     const double *cell_nu /* null, or [n_cells][5]: the component-wise isotropic model */) {
   const int q = degree + 1, F = 5 * q * q * q;
   const int cpb = (q == 3) ? kP2Cells : kP3Cells, nw = (q == 3) ? kP2Warps : kP3Warps;
@@ -95,7 +95,10 @@ int emu_stage(int degree, int scheme, int riemann, int64_t n_nodes, const double
     grad.assign((size_t)nt * N * 15 * kTile, 0.0);
     hn.assign((size_t)nt * 6 * q * q * 15 * kTile, 0.0);
     h2s = ToTiles(mesh.h2s, 18, nc, nt);
-    if (q == 3) RunTraceOnHost<3>(uin.data(), geom.data(), grad.data(), hn.data(), (int)nc);
+    const bool klocal = viscous[4] != 0;
+    if (q == 3 && klocal) RunTraceOnHost<3, true>(uin.data(), geom.data(), grad.data(), hn.data(), (int)nc);
+    else if (q == 3) RunTraceOnHost<3>(uin.data(), geom.data(), grad.data(), hn.data(), (int)nc);
+    else if (klocal) RunTraceOnHost<4, true>(uin.data(), geom.data(), grad.data(), hn.data(), (int)nc);
     else RunTraceOnHost<4>(uin.data(), geom.data(), grad.data(), hn.data(), (int)nc);
     a.grad = grad.data(); a.hn = hn.data(); a.h2s = h2s.data();
     a.vis.beta0 = viscous[0]; a.vis.beta1 = viscous[1]; a.vis.nu = viscous[2];

@@ -148,14 +148,14 @@ def test_sod_driver_dgfem_through_cpp_template_api(tmp_path, limiter):
     assert np.abs(got - ref).max() / np.abs(ref).max() < (1e-11 if limiter else 1e-12)
 
 
-def _cavity_reference(n, n_steps):
+def _cavity_reference(n, n_steps, k_local=False):
     """demo/laminar/cavity.cpp's loop on the CPU checker (Navier-Stokes + direct DG, no-slip walls)."""
     m = meshmod.box(n, n, 2, hi=(1.0, 1.0, 0.25))
     ic = [1.0, 0, 0, 0, (1.0 / (1.4 * 0.04)) / 0.4]
     moving, fixed = [0, 1.0, 0, 0, 0], [0, 0, 0, 0, 0]
     walls = {meshmod.XMIN: fixed, meshmod.XMAX: fixed, meshmod.YMIN: fixed, meshmod.YMAX: moving}
     if refapi.available(2):
-        r = refapi.Ref(m, degree=2, scheme=refapi.FR_VISCOUS, riemann=1)
+        r = refapi.Ref(m, degree=2, scheme=refapi.FR_LOCAL_VISCOUS if k_local else refapi.FR_VISCOUS, riemann=1)
         r.set_viscous(2.0, 1.0 / 12, 0.01, 0.708)
         for tag, val in walls.items():
             r.set_bc(tag, refapi.NO_SLIP, refapi.F_CONST, val)
@@ -175,6 +175,10 @@ def _cavity_reference(n, n_steps):
     for tag in (meshmod.ZMIN, meshmod.ZMAX):
         o.set_bc(tag, 0)
     u = o.approximate(oc.F_CONST, ic)
+    if k_local:
+        det = o.jacobian_determinants()
+        o.set_local(True)
+        u = (u.reshape(-1, 27, 5) * det[:, :, None]).reshape(-1)
     t = 0.0
     for _ in range(n_steps):
         dt = o.time_step(u, 1e-3, 3)
@@ -183,11 +187,13 @@ def _cavity_reference(n, n_steps):
     return u
 
 
-def test_lid_driven_cavity_driver_through_cpp_template_api(tmp_path):
+@pytest.mark.parametrize("k_local", [True, False])
+def test_lid_driven_cavity_driver_through_cpp_template_api(tmp_path, k_local):
     """ConvectionDiffusion<rotated::Euler<HLLC>, Direct<NavierStokes>> named exactly as demo/laminar/shockless.hpp
     names it; SetBetaValues / SetProperty / SetNoSlipWall as demo/laminar/cavity.cpp calls them."""
     exe = tmp_path / "cavity"
-    subprocess.check_call(["g++", "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"),
+    subprocess.check_call(["g++", *([] if k_local else ["-DKLOCAL_FALSE"]), "-std=c++20", "-O2", "-I",
+                           os.path.join(ROOT, "include"),
                            os.path.join(ROOT, "demo", "laminar", "cavity.cpp"), "-o", str(exe),
                            "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200",
                            "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")])
@@ -196,7 +202,7 @@ def test_lid_driven_cavity_driver_through_cpp_template_api(tmp_path):
     res = subprocess.run([str(exe), str(n_steps), str(out), str(n)], capture_output=True, text=True, timeout=300)
     assert res.returncode == 0, res.stdout + res.stderr
     got = np.fromfile(out, dtype=np.float64)
-    ref = _cavity_reference(n, n_steps)
+    ref = _cavity_reference(n, n_steps, k_local)
     assert got.shape == ref.shape == (n * n * 2 * 135,)
-    assert np.abs(got[1::5]).max() > 1e-4      # the lid has set the fluid in motion
+    assert np.abs(got[1::5]).max() > 1e-7      # the lid has set the fluid in motion (det-scaled when kLocal)
     assert np.abs(got - ref).max() / np.abs(ref).max() < 1e-12

@@ -169,6 +169,27 @@ def test_energy_viscosity_kernel_source_on_host_matches_golden(name, degree, rie
     assert min(1.0, cfl * min_dt) == pytest.approx(float(g["dt"]), rel=1e-13)
 
 
+@pytest.mark.parametrize("name,degree,riemann,viscous", cases.LOCAL_GOLDEN_CASES)
+def test_klocal_kernel_source_on_host_matches_golden(name, degree, riemann, viscous):
+    """The device keeps u = U / det; only the traces interpolate U.  Residual columns are det du/dt."""
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    m = meshmod.HexMesh(nodes=g["nodes"], cells=g["cells"], bfaces=g["bfaces"], btags=g["btags"])
+    det = g["det"]
+    u = (g["u"].reshape(det.shape + (5,)) / det[:, :, None]).reshape(-1)
+    holder, hf, tags, pts = emuapi.boundary(m, degree)
+    kinds = cases.VISCOUS_BCS if viscous else cases.MIXED_BCS
+    bv = np.zeros(pts.shape[:2] + (5,))
+    for tag, kind in kinds.items():
+        sel = tags == tag
+        f = cases.viscous_bc_function(kind) if viscous else cases.bc_function(kind)
+        bv[sel] = f(pts[sel], cases.GOLDEN_T)
+    kw = dict(tag_kinds=kinds, bvals=bv)
+    if viscous:
+        kw["viscous"] = list(cases.VISCOUS) + [1.0]
+    res = emuapi.stage(m, degree, 0, riemann, u, **kw)
+    assert relerr((res.reshape(det.shape + (5,)) * det[:, :, None]).reshape(-1), g["residual"]) < 1e-12
+
+
 @pytest.mark.parametrize("name,degree,riemann", cases.DGM_GOLDEN_CASES)
 def test_dg_general_kernel_source_on_host_matches_golden(name, degree, riemann):
     g = np.load(os.path.join(GOLDEN, name + ".npz"))

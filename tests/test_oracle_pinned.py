@@ -234,6 +234,22 @@ def test_c_oracle_dg_general_weno_lazy_matches_golden(name, degree, riemann):
     assert relerr(o.rk_update(limited, 3, 0.0, cases.GOLDEN_DT), g["u_rk3"]) < TOL
 
 
+@pytest.mark.parametrize("name,degree,riemann,viscous", cases.LOCAL_GOLDEN_CASES)
+def test_c_oracle_klocal_matches_golden(name, degree, riemann, viscous):
+    """Hexahedron<..., true>: columns hold det(J) u; gradients and Hessians of that interpolant; dU/dt residuals."""
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    o = oc.Oracle(_golden_mesh(g), degree, 3 if viscous else 0, riemann)
+    if viscous:
+        cases.apply_viscous_oracle(o)
+    else:
+        cases.apply_bcs_oracle(o)
+    assert relerr(o.jacobian_determinants(), g["det"]) < 1e-14
+    o.set_local(True)
+    assert relerr(o.residual(g["u"], cases.GOLDEN_T), g["residual"]) < TOL
+    assert o.time_step(g["u"], 1.0, 3) == pytest.approx(float(g["dt"]), rel=1e-14)
+    assert relerr(o.rk_update(g["u"], 3, 0.0, cases.GOLDEN_DT), g["u_rk3"]) < TOL
+
+
 def _flux_1d(rho, u, p):
     """Flux of a 1-D primitive state (test/riemann/euler/exact.cpp:34-39)."""
     e = p / 0.4 + 0.5 * rho * u * u
