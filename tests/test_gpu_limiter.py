@@ -253,3 +253,20 @@ def test_weno_eigen_two_parts_match_the_reference_parts():
         sp.ctx.limiter_weno_eigen(*cases.WENO, 1)
     for k, sp in enumerate(S):
         assert relerr(sp.GetSolutionColumn(), r.get_solution(k)) < TOL
+
+
+def test_dg_lobatto_with_weno_lazy_vs_oracle():
+    """BASELINE config 3's combination: dg::Lobatto + Extrapolation + weno::Lazy(1e-3, 1e-6)."""
+    m = cases.small_mesh(seed=31)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, 2), seed=5, amp=1e-2)
+    o = oc.Oracle(m, 2, 1, 1)
+    cases.apply_bcs_oracle(o)
+    o.set_limiter(*cases.WENO)
+    limited = o.weno_lazy(u, *cases.WENO)
+    sp = Spatial(Part(m), scheme=capi.DG_LOBATTO, degree=2, riemann=capi.HLLC, device=0)
+    cases.apply_bcs_spatial(sp, cases.MIXED_BCS)
+    sp.SetLimiter(*cases.WENO)
+    sp.SetSolutionColumn(u)
+    assert relerr(sp.GetSolutionColumn(), limited) < TOL
+    RungeKutta(3).Update(sp, 0.0, 1e-3)
+    assert relerr(sp.GetSolutionColumn(), o.rk_update(limited, 3, 0.0, 1e-3)) < TOL
