@@ -185,8 +185,9 @@ int mcfd_set_cell_viscosity(mcfd_ctx *ctx, int64_t n_cells, const double *nu);
 int mcfd_get_cell_viscosity(mcfd_ctx *ctx, double *nu);   /* [n_local + n_ghost][5] */
 
 /* EnergyBasedViscosity (include/mini/spatial/viscosity.hpp) + WithViscosity (with_viscosity.hpp:20-73) on
- * MCFD_CELL_VISCOSITY_DDG contexts without ghost cells (the reference keeps this state in class statics: one spatial
- * object per process).
+ * MCFD_CELL_VISCOSITY_DDG contexts (the reference keeps this state in class statics: one spatial object per process;
+ * here it is per context).  On a part with ghost cells UpdateProperties reads whatever the ghost cells hold at the time
+ * of the call — the reference calls it from SetSolutionColumn, i.e. before the new state has been exchanged.
  * mcfd_build_damping_matrices = EnergyBasedViscosity::Initialize / BuildDampingMatrices (viscosity.hpp:299-384,
  * 549-554): per cell the N x N matrix of the viscous operator (nu = 1, zero on the far side of every face) applied to
  * the unit nodal vectors, rows scaled by the quadrature weights; built from N probe launches of the trace and stage
@@ -196,6 +197,14 @@ int mcfd_get_cell_viscosity(mcfd_ctx *ctx, double *nu);   /* [n_local + n_ghost]
  * residual reads: face-jump integrals (IntegrateJumpOnFaces, :446-475), then per cell and component
  * nu = clamp(jump / (-u^T D u * h / lambda_max * time_scale)) or 0 below the reference value (GetViscosityValues,
  * :477-544).  WithViscosity calls it after every SetSolutionColumn (with_viscosity.hpp:52-55). */
+/* EnergyBasedViscosity::ShareGhostCellProperties / UpdateGhostCellProperties (viscosity.hpp:163-189; called by
+ * WithViscosity::GetResidualColumn before every residual, with_viscosity.hpp:45-50): 5 doubles per cell, the send cells'
+ * viscosities packed into the send buffer / the receive buffer unpacked into the ghost cells, in the order of
+ * mcfd_set_halo.  As with the state, moving the bytes between the parts is the host's job. */
+int mcfd_viscosity_halo_buffers(mcfd_ctx *ctx, double **send_dev, int64_t *send_doubles, double **recv_dev,
+                                int64_t *recv_doubles);
+int mcfd_viscosity_halo_pack(mcfd_ctx *ctx);
+int mcfd_viscosity_halo_unpack(mcfd_ctx *ctx);
 int mcfd_build_damping_matrices(mcfd_ctx *ctx);
 int mcfd_get_damping_matrices(mcfd_ctx *ctx, double *matrices);   /* [n_local][N][N], row-major */
 int mcfd_update_cell_viscosity(mcfd_ctx *ctx, double time_scale);

@@ -56,6 +56,9 @@ SYMBOLS = {
     "mcfd_set_diffusion": (C.c_int, [_P, C.c_double, C.c_double, C.c_double, C.c_double]),
     "mcfd_set_cell_viscosity": (C.c_int, [_P, C.c_int64, _D]),
     "mcfd_get_cell_viscosity": (C.c_int, [_P, _D]),
+    "mcfd_viscosity_halo_buffers": (C.c_int, [_P, C.POINTER(_P), _I64, C.POINTER(_P), _I64]),
+    "mcfd_viscosity_halo_pack": (C.c_int, [_P]),
+    "mcfd_viscosity_halo_unpack": (C.c_int, [_P]),
     "mcfd_build_damping_matrices": (C.c_int, [_P]),
     "mcfd_get_damping_matrices": (C.c_int, [_P, _D]),
     "mcfd_update_cell_viscosity": (C.c_int, [_P, C.c_double]),
@@ -164,6 +167,18 @@ class Context:
     def set_diffusion(self, beta_0, beta_1, nu, prandtl):
         self._check(self.lib.mcfd_set_diffusion(self.h, beta_0, beta_1, nu, prandtl))
 
+    def viscosity_halo_buffers(self):
+        sp, rp = _P(), _P()
+        sn, rn = C.c_int64(0), C.c_int64(0)
+        self._check(self.lib.mcfd_viscosity_halo_buffers(self.h, C.byref(sp), C.byref(sn), C.byref(rp), C.byref(rn)))
+        return (sp.value or 0, sn.value), (rp.value or 0, rn.value)
+
+    def viscosity_halo_pack(self):
+        self._check(self.lib.mcfd_viscosity_halo_pack(self.h))
+
+    def viscosity_halo_unpack(self):
+        self._check(self.lib.mcfd_viscosity_halo_unpack(self.h))
+
     def build_damping_matrices(self):
         self._check(self.lib.mcfd_build_damping_matrices(self.h))
 
@@ -177,9 +192,10 @@ class Context:
         self._check(self.lib.mcfd_update_cell_viscosity(self.h, time_scale))
 
     def cell_viscosity(self, n_cells=None):
-        out = np.empty((self.n_local if n_cells is None else n_cells, 5))
+        """[n_local][5] by default; pass n_local + n_ghost to see the ghost cells' values too."""
+        out = np.empty((self.n_cells, 5))        # the library always writes local and ghost cells
         self._check(self.lib.mcfd_get_cell_viscosity(self.h, _dp(out)))
-        return out
+        return out[:self.n_local if n_cells is None else n_cells].copy()
 
     def jacobian_determinants(self):
         out = np.empty((self.n_local, self.q ** 3))
@@ -232,6 +248,7 @@ class Context:
                                            len(bface_nodes), _ip(bface_nodes), _i32(bface_tags),
                                            0 if pairs is None else len(pairs), _ip(pairs)))
         self.n_local = n_local
+        self.n_cells = n_local + n_ghost
 
     def faces(self, kind):
         n = self.lib.mcfd_get_faces(self.h, kind, None, None, None, None, None)

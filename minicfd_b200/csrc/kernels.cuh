@@ -2037,6 +2037,17 @@ __global__ void ConvertKernel(double *tiles, double *column, const int *cells, i
   }
 }
 
+// Ghost exchange of the per-cell viscosities (EnergyBasedViscosity::ShareGhostCellProperties /
+// UpdateGhostCellProperties, spatial/viscosity.hpp:163-189): 5 doubles per cell, buffer[i][5] <-> nu[tile][comp][lane]
+__global__ void ViscosityHaloKernel(double *nu, double *buffer, const int *cells, int n_items, int unpack) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_items * 5) return;
+  const int cell = cells[i / 5], k = i % 5;
+  double *at = nu + ((size_t)(cell >> 5) * 5 + k) * kTile + (cell & 31);
+  if (unpack) *at = buffer[i];
+  else buffer[i] = *at;
+}
+
 // Test hook: n independent rotated Riemann problems.
 template <int kRiemann>
 __global__ void RiemannKernel(int bc_kind, int n, const double *normals, const double *ul,

@@ -57,6 +57,7 @@ struct mcfd_ctx {
   DevBuf<double> damping;                       // EnergyBasedViscosity: [tile][r*N + c][lane] damping matrices
   DevBuf<unsigned long long> visc_dt_bits;      // min_dt_ of the last mcfd_update_cell_viscosity
   bool energy_viscosity = false;                // WithViscosity mode: the time step comes from min_dt_
+  DevBuf<double> nu_send, nu_recv;              // packed viscosities of the send / ghost cells (5 doubles per cell)
   DevBuf<double> bas, mod, tay, mod_new, tay_new;   // WENO limiter: per-cell bases and modal coefficients
   DevBuf<double> frames, weno_scratch;          // weno::Eigen: face frames, per-CTA candidate scratch
   std::vector<int64_t> global_ids;              // optional, for the next mcfd_set_mesh
@@ -680,7 +681,6 @@ int mcfd_build_damping_matrices(mcfd_ctx *ctx) {
   if (ctx->cfg.diffusion != MCFD_CELL_VISCOSITY_DDG)
     return Fail(ctx, MCFD_ERR_STATE, "the context was not created with MCFD_CELL_VISCOSITY_DDG");
   if (ctx->rk_order) return Fail(ctx, MCFD_ERR_STATE, "an RK step is open");
-  if (ctx->mesh.n_ghost) return Fail(ctx, MCFD_ERR_STATE, "the energy-based viscosity is built for parts without ghost cells");
   const int n = ctx->n_nodes;
   const size_t state = (size_t)ctx->n_tiles * ctx->fields * kTile;
   MCFD_CUDA(ctx, ctx->damping.Alloc((size_t)ctx->n_tiles * n * n * kTile));
@@ -731,6 +731,33 @@ int mcfd_update_cell_viscosity(mcfd_ctx *ctx, double time_scale) {
   ctx->launches += 2;
   return MCFD_OK;
 }
+
+int mcfd_viscosity_halo_buffers(mcfd_ctx *ctx, double **send_dev, int64_t *send_doubles, double **recv_dev,
+    int64_t *recv_doubles) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (!ctx->cell_nu.p) return Fail(ctx, MCFD_ERR_STATE, "no per-cell viscosity in this context");
+  if (ctx->nu_send.n != ctx->send_cells.n * 5) MCFD_CUDA(ctx, ctx->nu_send.Alloc(ctx->send_cells.n * 5));
+  if (ctx->nu_recv.n != ctx->recv_cells.n * 5) MCFD_CUDA(ctx, ctx->nu_recv.Alloc(ctx->recv_cells.n * 5));
+  if (send_dev) *send_dev = ctx->nu_send.p;
+  if (send_doubles) *send_doubles = (int64_t)ctx->nu_send.n;
+  if (recv_dev) *recv_dev = ctx->nu_recv.p;
+  if (recv_doubles) *recv_doubles = (int64_t)ctx->nu_recv.n;
+  return MCFD_OK;
+}
+
+static int ViscosityHalo(mcfd_ctx *ctx, int unpack) {
+  if (int s = mcfd_viscosity_halo_buffers(ctx, nullptr, nullptr, nullptr, nullptr)) return s;
+  const int n = (int)(unpack ? ctx->recv_cells.n : ctx->send_cells.n);
+  if (n == 0) return MCFD_OK;
+  ViscosityHaloKernel<<<(n * 5 + 127) / 128, 128, 0, ctx->stream>>>(ctx->cell_nu.p, unpack ? ctx->nu_recv.p : ctx->nu_send.p,
+      unpack ? ctx->recv_cells.p : ctx->send_cells.p, n, unpack);
+  MCFD_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  return MCFD_OK;
+}
+
+int mcfd_viscosity_halo_pack(mcfd_ctx *ctx) { return ViscosityHalo(ctx, 0); }
+int mcfd_viscosity_halo_unpack(mcfd_ctx *ctx) { return ViscosityHalo(ctx, 1); }
 
 int mcfd_get_cell_viscosity(mcfd_ctx *ctx, double *nu) {
   if (int s = RequireMesh(ctx)) return s;

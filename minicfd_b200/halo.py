@@ -33,6 +33,7 @@ class HaloExchanger:
         self._reqs = []
         self._ops = None
         self.inflight = False     # an exchange of the current state has been posted and not yet unpacked
+        self.received = False     # the receive buffer holds the neighbours' values of some earlier state
         self._pack = self._unpack = lambda: None
 
     def bind(self, send: torch.Tensor, recv: torch.Tensor, pack=None, unpack=None):
@@ -52,6 +53,15 @@ class HaloExchanger:
         recv = torch.as_tensor(_DeviceArray(rp, rn), device=dev) if rn else torch.empty(0, dtype=torch.float64, device=dev)
         ctx.set_stream(torch.cuda.current_stream().cuda_stream)
         self.bind(send, recv, ctx.halo_pack, ctx.halo_unpack)
+
+    def attach_viscosity(self, spatial):
+        """The same for the per-cell viscosities (5 doubles per cell): mcfd_viscosity_halo_*."""
+        ctx = spatial.ctx
+        (sp, sn), (rp, rn) = ctx.viscosity_halo_buffers()
+        dev = torch.device("cuda", torch.cuda.current_device())
+        send = torch.as_tensor(_DeviceArray(sp, sn), device=dev) if sn else torch.empty(0, dtype=torch.float64, device=dev)
+        recv = torch.as_tensor(_DeviceArray(rp, rn), device=dev) if rn else torch.empty(0, dtype=torch.float64, device=dev)
+        self.bind(send, recv, ctx.viscosity_halo_pack, ctx.viscosity_halo_unpack)
 
     def _build_ops(self):
         ops = []
@@ -76,6 +86,7 @@ class HaloExchanger:
         self._reqs = []
         self._unpack()
         self.inflight = False
+        self.received = True
 
     def exchange(self):
         """Make the ghost cells of the current state current (reuses an exchange already in flight)."""

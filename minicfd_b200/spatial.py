@@ -86,14 +86,30 @@ class Spatial:
     def EnableEnergyBasedViscosity(self, time_scale=1.0):
         """Makes this object behave like `WithViscosity<General>` over `EnergyBasedViscosity<Part, Riemann>`
         (spatial/with_viscosity.hpp:20-73, demo/euler/sourceless.hpp:82-103): damping matrices now
-        (Viscosity::Initialize), UpdateProperties after every SetSolutionColumn and Runge-Kutta stage, and the time
-        step from its min_dt_.  Single part only, like the reference's class statics."""
-        assert self.comm is None and self.part.n_ghost == 0
+        (Viscosity::Initialize), UpdateProperties after every SetSolutionColumn and Runge-Kutta stage (with whatever
+        the ghost cells hold then, like the reference), the ghost viscosities exchanged before every residual, and the
+        time step from its min_dt_."""
         self.ctx.build_damping_matrices()
         self._energy_time_scale = float(time_scale)
+        self._nu_comm = None
+        if self.comm is not None:          # ShareGhostCellProperties / UpdateGhostCellProperties: 5 doubles per cell
+            from . import halo
+            self._nu_comm = halo.for_part(self.part, 5, self.comm.group)
+            self._nu_comm.attach_viscosity(self)
+
+    def ShareViscosity(self):
+        """with_viscosity.hpp:45-50: the ghost cells' viscosities before a residual."""
+        if getattr(self, "_nu_comm", None) is not None:
+            self._nu_comm.exchange()
 
     def UpdateProperties(self):
+        """EnergyBasedViscosity::UpdateProperties (viscosity.hpp:556-572).  The reference does not exchange anything
+        here: the jumps on ghost faces use the ghost cells' coefficients as last received.  The stages write into
+        alternating state buffers, so those values are unpacked (again) into the buffer that is current now."""
         if getattr(self, "_energy_time_scale", None) is not None:
+            if self.comm is not None and self.comm.received:
+                self.comm.drain()
+                self.ctx.halo_unpack()
             self.ctx.update_cell_viscosity(self._energy_time_scale)
 
     def SetCellViscosity(self, nu):
@@ -159,6 +175,7 @@ class Spatial:
         """fem.hpp:248-258: halo exchange, then volume + face + boundary terms (one fused kernel)."""
         if self.comm is not None:
             self.comm.exchange()
+        self.ShareViscosity()
         return self.ctx.residual(self._t)
 
     def GetTimeStep(self, dt_guess, rk_order):
@@ -215,6 +232,7 @@ class RungeKutta:
         for stage in range(self.order):
             if comm is not None:
                 comm.exchange()
+            system.ShareViscosity()
             ctx.rk_stage_inner(stage)
             ctx.rk_stage_inter(stage)
             system.Reconstruct()

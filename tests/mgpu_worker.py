@@ -19,13 +19,86 @@ from minicfd_b200.part import Part, cell_points  # noqa: E402
 from minicfd_b200.spatial import RungeKutta, Spatial  # noqa: E402
 
 
+def finish(comm, ok, rank):
+    flag = torch.tensor([1.0 if ok else 0.0], device="cuda")
+    dist.broadcast(flag, 0)
+    comm.drain(); torch.cuda.synchronize()
+    dist.destroy_process_group()
+    if flag.item() != 1.0:
+        sys.exit(1)
+    if rank == 0:
+        print("MGPU OK")
+
+
+def energy(sp, comm, m, parts, part, degree, rank, world):
+    """WithViscosity<fr::Lobatto> over EnergyBasedViscosity on N parts: UpdateProperties after every stage sees the
+    ghost cells' coefficients of the stage INPUT (with_viscosity.hpp:56-59 does no exchange), the viscosities are
+    exchanged before the next residual (with_viscosity.hpp:47-51).  Rank 0 replays exactly that with the single-part
+    CPU checker: the viscosity of a cell depends on the cell and its face neighbours only."""
+    kf = 5 * (degree + 1) ** 3
+    for tag in range(6):
+        sp.SetInviscidWall(tag)
+    sp.SetDiffusion(*cases.ENERGY_BETAS, 0.0, 0.708)
+    sp.EnableEnergyBasedViscosity()
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), seed=4, amp=cases.ENERGY_AMP)
+    local = part.gather_from_global(u, kf)
+    sp.SetSolutionColumn(local)
+    sp.GetResidualColumn()                  # brings the ghost cells up to date ...
+    sp.SetSolutionColumn(local)             # ... so that the first UpdateProperties sees them
+    dt, n_steps = 1e-3, 2
+    for k in range(n_steps):
+        RungeKutta(3).Update(sp, k * dt, dt)
+    sol = torch.from_numpy(np.zeros(m.n_cells * kf))
+    nus = torch.from_numpy(np.zeros(m.n_cells * 5))
+    part.scatter_to_global(sp.GetSolutionColumn(), kf, sol.numpy())
+    part.scatter_to_global(sp.ctx.cell_viscosity().reshape(-1), 5, nus.numpy())
+    sol, nus = sol.cuda(), nus.cuda()
+    dist.all_reduce(sol)
+    dist.all_reduce(nus)
+    ok = True
+    if rank == 0:
+        o = oc.Oracle(m, degree, 6, 1)
+        for tag in range(6):
+            o.set_bc(tag, 0)
+        o.set_viscous(*cases.ENERGY_BETAS, 0.0, 0.708)
+        damping = o.damping_matrices()
+        owned = [Part(m, parts, k, world).local_global for k in range(world)]
+
+        def properties(new, old):
+            nu = np.zeros((m.n_cells, 5))
+            for cells in owned:
+                mix = old.reshape(m.n_cells, kf).copy()
+                mix[cells] = new.reshape(m.n_cells, kf)[cells]
+                nu[cells] = o.update_viscosity(mix.reshape(-1), damping)[0][cells]
+            o.set_cell_viscosity(nu)
+            return nu
+
+        u0 = u.reshape(-1).copy()
+        nu = properties(u0, u0)
+        assert 0 < (nu > 0).sum() < nu.size
+        for k in range(n_steps):
+            t = k * dt
+            u1 = u0 + dt * o.residual(u0, t)
+            properties(u1, u0)
+            u2 = (u0 * 3 + u1 + dt * o.residual(u1, t + dt)) / 4
+            properties(u2, u1)
+            u3 = (u0 + 2 * (u2 + dt * o.residual(u2, t + dt / 2))) / 3
+            nu = properties(u3, u2)
+            u0 = u3
+        e_u = np.abs(sol.cpu().numpy() - u0).max() / np.abs(u0).max()
+        e_n = np.abs(nus.cpu().numpy().reshape(-1, 5) - nu).max() / np.abs(nu).max()
+        print(f"MGPU world={world} degree={degree} energy: solution rel err {e_u:.2e}, viscosity rel err {e_n:.2e}")
+        ok = e_u < 1e-11 and e_n < 1e-9
+    finish(comm, ok, rank)
+
+
 def main():
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
     torch.cuda.set_device(local)
     os.environ.setdefault("TORCH_NCCL_HIGH_PRIORITY", "1"); dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     degree = int(sys.argv[1]) if len(sys.argv) > 1 else 2
-    mode = sys.argv[2] if len(sys.argv) > 2 else "euler"     # euler | viscous | weno
+    mode = sys.argv[2] if len(sys.argv) > 2 else "euler"     # euler | viscous | weno | energy
     px, py, pz = meshmod.factor3(world)
     m = meshmod.box(4 * px, 4 * py, 3 * pz, warp=0.1, seed=3)
     parts = meshmod.block_partition(m, px, py, pz)
@@ -33,7 +106,9 @@ def main():
     kf = 5 * (degree + 1) ** 3
     comm = halo.for_part(part, kf)
     sp = Spatial(part, degree=degree, riemann=capi.HLLC, device=local, comm=comm,
-                 diffusion=capi.NAVIER_STOKES_DDG if mode == "viscous" else capi.INVISCID)
+                 diffusion={"viscous": capi.NAVIER_STOKES_DDG, "energy": capi.CELL_VISCOSITY_DDG}.get(mode, capi.INVISCID))
+    if mode == "energy":
+        return energy(sp, comm, m, parts, part, degree, rank, world)
     if mode == "viscous":
         cases.apply_viscous_spatial(sp)
     else:
@@ -101,14 +176,7 @@ def main():
         e_r = np.abs(res.cpu().numpy() - rref).max() / np.abs(rref).max()
         print(f"MGPU world={world} degree={degree}: solution rel err {e_u:.2e}, residual rel err {e_r:.2e}")
         ok = e_u < 1e-12 and e_r < 1e-11
-    flag = torch.tensor([1.0 if ok else 0.0], device="cuda")
-    dist.broadcast(flag, 0)
-    comm.drain(); torch.cuda.synchronize()
-    dist.destroy_process_group()
-    if flag.item() != 1.0:
-        sys.exit(1)
-    if rank == 0:
-        print("MGPU OK")
+    finish(comm, ok, rank)
 
 
 if __name__ == "__main__":

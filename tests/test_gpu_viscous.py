@@ -254,3 +254,78 @@ def test_fr_general_with_navier_stokes(degree, c_next, riemann):
     assert sp.GetTimeStep(1.0, 3) == pytest.approx(o.time_step(u, 1.0, 3), rel=1e-13)
     RungeKutta(3).Update(sp, 0.0, 1e-3)
     assert relerr(sp.GetSolutionColumn(), o.rk_update(u, 3, 0.0, 1e-3)) < TOL
+
+
+def test_energy_based_viscosity_two_parts_with_halo_buffers():
+    """Two parts on one GPU: damping matrices with ghost cells present, UpdateProperties over ghost faces, and the ghost
+    cells' viscosities through mcfd_viscosity_halo_*.  With the new state exchanged BEFORE every UpdateProperties the
+    result does not depend on the partition and equals the single-part oracle."""
+    import torch
+    from minicfd_b200.halo import _DeviceArray
+    m = meshmod.scramble(meshmod.box(6, 4, 2, warp=0.1, seed=2), seed=3)
+    parts = (np.arange(m.n_cells) * 2 // m.n_cells).astype(np.int32)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, 2), seed=9, amp=cases.ENERGY_AMP)
+    o = oc.Oracle(m, 2, 6, 1)
+    for tag in range(6):
+        o.set_bc(tag, 0)
+    o.set_viscous(*cases.ENERGY_BETAS, 0.0, 0.708)
+    damping = o.damping_matrices()
+    dt = 1e-3
+    def set_solution(uu):
+        nu, _ = o.update_viscosity(uu, damping)
+        o.set_cell_viscosity(nu)
+        return uu, nu
+    u0, nu0 = set_solution(u)
+    assert 0 < (nu0 > 0).sum() < nu0.size
+    u1, _ = set_solution(u0 + dt * o.residual(u0, 0.0))
+    u2, _ = set_solution((u0 * 3 + u1 + dt * o.residual(u1, dt)) / 4)
+    u3, nu3 = set_solution((u0 + 2 * (u2 + dt * o.residual(u2, dt / 2))) / 3)
+
+    P = [Part(m, parts, r, 2) for r in range(2)]
+    S = [Spatial(p, degree=2, riemann=capi.HLLC, device=0, diffusion=capi.CELL_VISCOSITY_DDG) for p in P]
+    for sp in S:
+        for tag in range(6):
+            sp.SetInviscidWall(tag)
+        sp.SetDiffusion(*cases.ENERGY_BETAS, 0.0, 0.708)
+        sp.ctx.build_damping_matrices()
+    for sp, p in zip(S, P):
+        assert relerr(sp.ctx.damping_matrices(), damping[p.local_global]) < TOL
+    ubuf = [sum(sp.ctx.halo_buffers(), ()) for sp in S]
+    nbuf = [sum(sp.ctx.viscosity_halo_buffers(), ()) for sp in S]
+
+    def copy(bufs):
+        torch.cuda.synchronize()
+        for a, b in ((0, 1), (1, 0)):
+            src = torch.as_tensor(_DeviceArray(bufs[a][0], bufs[a][1]), device="cuda")
+            dst = torch.as_tensor(_DeviceArray(bufs[b][2], bufs[b][3]), device="cuda")
+            dst.copy_(src)
+        torch.cuda.synchronize()
+
+    def refresh():                      # new state to the ghosts, UpdateProperties, viscosities to the ghosts
+        for sp in S:
+            sp.ctx.halo_pack()
+        copy(ubuf)
+        for sp in S:
+            sp.ctx.halo_unpack()
+            sp.ctx.update_cell_viscosity(1.0)
+            sp.ctx.viscosity_halo_pack()
+        copy(nbuf)
+        for sp in S:
+            sp.ctx.viscosity_halo_unpack()
+
+    for sp, p in zip(S, P):
+        sp.ctx.set_solution(p.gather_from_global(u, 135))
+    refresh()
+    for sp, p in zip(S, P):
+        nu = sp.ctx.cell_viscosity(p.n_local + p.n_ghost)
+        assert relerr(nu, nu0[p.global_ids]) < TOL          # local AND ghost cells
+    for sp in S:
+        sp.ctx.rk_begin(3, 0.0, dt)
+    for stage in range(3):
+        for sp in S:
+            sp.ctx.rk_stage_inner(stage)
+            sp.ctx.rk_stage_inter(stage)
+        refresh()
+    for sp, p in zip(S, P):
+        assert relerr(sp.GetSolutionColumn().reshape(-1, 135), u3.reshape(-1, 135)[p.local_global]) < 1e-11
+        assert relerr(sp.ctx.cell_viscosity(), nu3[p.local_global]) < 1e-9
