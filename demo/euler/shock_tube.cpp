@@ -5,6 +5,7 @@
 // Differences from the reference driver: the mesh is a structured box built in memory instead of
 // gmsh -> CGNS -> METIS (out of scope), and there is no JSON / CGNS / VTK I/O.
 // Prints the solution column's L1 norm per component and writes the final column to a binary file.
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <string>
@@ -68,6 +69,20 @@ using Limiter = mini::limiter::weno::Eigen<Cell, Riemann>;
 using Limiter = mini::limiter::weno::Lazy<Cell>;
 #endif
 using Spatial = mini::spatial::WithLimiter<General, Limiter>;
+#elif defined(VISCOSITY)   // demo/euler/sourceless.hpp:82-103
+#include "mini/riemann/concept.hpp"
+#include "mini/riemann/diffusive/linear.hpp"
+#include "mini/riemann/diffusive/direct.hpp"
+#include "mini/spatial/viscosity.hpp"
+#include "mini/spatial/with_viscosity.hpp"
+#include "mini/limiter/average.hpp"
+#include "mini/limiter/majority.hpp"
+using Diffusion = mini::riemann::diffusive::Direct<mini::riemann::diffusive::Isotropic<Scalar, kComponents>>;
+using RiemannWithViscosity = mini::spatial::EnergyBasedViscosity<Part,
+    mini::riemann::ConvectionDiffusion<Riemann, Diffusion>>;
+static_assert(mini::riemann::ConvectiveDiffusive<RiemannWithViscosity>);
+using General = mini::spatial::fr::Lobatto<Part, RiemannWithViscosity>;
+using Spatial = mini::spatial::WithViscosity<General>;
 #else
 using Spatial = Unlimited;
 #endif
@@ -119,6 +134,11 @@ int main(int argc, char *argv[]) {
   auto face_to_riemanns = [&spatial](Face const &face) -> auto const & { return spatial.GetRiemannSolvers(face); };
   spatial.limiter_ptr()->InstallRiemannSolvers(face_to_riemanns);
 #endif
+#elif defined(VISCOSITY)   // demo/euler/sourceless.cpp:117-126
+  Diffusion::SetProperty(0.0);
+  Diffusion::SetBetaValues(/* ddg_beta_0 = */2.0, /* ddg_beta_1 = */1.0 / 12);
+  Spatial spatial(&part);
+  RiemannWithViscosity::SetTimeScale(/* time_scale = */1.0);
 #else
   Spatial spatial(&part);
 #endif
@@ -128,6 +148,10 @@ int main(int argc, char *argv[]) {
   auto cl = Gas::PrimitiveToConservative(left), cr = Gas::PrimitiveToConservative(right);
   for (int k = 0; k < 5; ++k) { given_value_left[k] = cl[k]; given_value_right[k] = cr[k]; }
   spatial.Approximate(MyIC);
+#ifdef VISCOSITY   // demo/euler/sourceless.cpp:145-153 with "initial_limiter": "average"
+  mini::limiter::average::Reconstruct(spatial.part_ptr());
+  RiemannWithViscosity::Viscosity::UpdateProperties();
+#endif
   // demo/euler/shock_tube.cpp:56-66
   spatial.SetSmartBoundary("Left", GivenLeft);
   spatial.SetSmartBoundary("Right", GivenRight);
@@ -143,6 +167,13 @@ int main(int argc, char *argv[]) {
   double l1[5] = {0, 0, 0, 0, 0};
   for (size_t i = 0; i < column.size(); ++i) l1[i % 5] += std::abs(column[i]);
   std::printf("t = %.6f after %d steps; sum|u_k| = %.15e %.15e %.15e %.15e %.15e\n", t, n_steps, l1[0], l1[1], l1[2], l1[3], l1[4]);
+#ifdef VISCOSITY   // what the reference writes as CellViscosity1..5 (demo/euler/sourceless.cpp:122-126)
+  double nu_max = 0;
+  for (int64_t c = 0; c < part.CountLocalCells(); ++c) {
+    for (int k = 0; k < kComponents; ++k) nu_max = std::max(nu_max, RiemannWithViscosity::GetPropertyOnCell(c, 0)[k]);
+  }
+  std::printf("max cell viscosity %.15e\n", nu_max);
+#endif
   if (out_name) {
     FILE *f = std::fopen(out_name, "wb");
     std::fwrite(column.data(), sizeof(double), column.size(), f);

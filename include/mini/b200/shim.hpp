@@ -185,10 +185,23 @@ struct NavierStokes {
   using Scalar = typename Gas::Scalar;
   static constexpr int kComponents = 5;
   static constexpr int kDimensions = 3;
+  static constexpr int kDiffusionTag = MCFD_NAVIER_STOKES_DDG;
   struct Property { Scalar nu, prandtl; };
   static void SetProperty(Scalar nu, Scalar prandtl) { property_ = Property{nu, prandtl}; }
   static Property const &GetProperty() { return property_; }
   inline static Property property_{0.0, 0.708};
+};
+// riemann/diffusive/linear.hpp:104-121: one viscosity for every component (F_k = -nu grad u_k), as a tag
+template <typename S, int K>
+struct Isotropic {
+  using Scalar = S;
+  static constexpr int kComponents = K;
+  static constexpr int kDimensions = 3;
+  static constexpr int kDiffusionTag = MCFD_CELL_VISCOSITY_DDG;
+  struct Property { Scalar nu, prandtl; };
+  static void SetProperty(Scalar nu) { property_ = Property{nu, 1.0}; }
+  static Property const &GetProperty() { return property_; }
+  inline static Property property_{0.0, 1.0};
 };
 // riemann/diffusive/direct.hpp:15-91
 template <class DiffusionModel>
@@ -199,6 +212,14 @@ struct Direct : DiffusionModel {
   inline static Scalar beta_0_ = 2.0, beta_1_ = 1.0 / 12;
 };
 }  // namespace diffusive
+
+// riemann/concept.hpp:41-91 on the tags: what a driver's static_assert can still check
+template <typename R>
+concept Convective = requires { typename R::Conservative; R::kKind; R::kComponents; R::kDimensions; };
+template <typename R>
+concept Diffusive = requires { typename R::Diffusion; } && (R::kDiffusion != MCFD_INVISCID);
+template <typename R>
+concept ConvectiveDiffusive = Convective<R> && Diffusive<R>;
 
 // riemann/concept.hpp:93-121
 template <class C, class D>
@@ -213,7 +234,7 @@ struct ConvectionDiffusion : C, D {
   static constexpr int kComponents = C::kComponents;
   static constexpr int kDimensions = C::kDimensions;
   static constexpr int kKind = C::kKind;
-  static constexpr int kDiffusion = MCFD_NAVIER_STOKES_DDG;
+  static constexpr int kDiffusion = D::kDiffusionTag;
 };
 }  // namespace riemann
 
@@ -301,6 +322,9 @@ class Part {
   std::unordered_map<std::string, int32_t> name_to_tag_;
   Halo halo_;
   Int n_local_ = 0, n_ghost_ = 0;
+  // the context of the spatial object built on this part: what `mini::limiter::Reconstruct(&part, ...)` and the
+  // like, which the reference hands a Part, act on
+  mcfd_ctx *context_ = nullptr;
 
  private:
   int rank_, size_;
@@ -417,10 +441,14 @@ class FiniteElementB200 : public temporal::System<typename P::Scalar> {
           (int32_t)h.recv_counts.size(), h.recv_counts.data(), h.recv_cells.data()), ctx_, "mcfd_set_halo");
     }
     b200::Check(mcfd_set_time_callback(ctx_, &FiniteElementB200::OnTime, this), ctx_, "mcfd_set_time_callback");
+    p.context_ = ctx_;
   }
   FiniteElementB200(const FiniteElementB200 &) = delete;
   FiniteElementB200 &operator=(const FiniteElementB200 &) = delete;
-  ~FiniteElementB200() noexcept override { mcfd_destroy(ctx_); }
+  ~FiniteElementB200() noexcept override {
+    if (part_ptr_->context_ == ctx_) part_ptr_->context_ = nullptr;
+    mcfd_destroy(ctx_);
+  }
 
   Part *part_ptr() const { return part_ptr_; }
   Part const &part() const { return *part_ptr_; }
@@ -505,7 +533,9 @@ class FiniteElementB200 : public temporal::System<typename P::Scalar> {
  private:
   // the reference reads its class statics at every flux evaluation; hand their current values over
   void PushDiffusion() const {
-    if constexpr (Riemann::kDiffusion != MCFD_INVISCID) {
+    if constexpr (requires { typename Riemann::Viscosity; }) {
+      // per-cell values owned by the viscosity rule; the betas went over when WithViscosity was constructed
+    } else if constexpr (Riemann::kDiffusion != MCFD_INVISCID) {
       using D = typename Riemann::Diffusion;
       b200::Check(mcfd_set_diffusion(ctx_, D::beta_0_, D::beta_1_, D::GetProperty().nu, D::GetProperty().prandtl),
           ctx_, "mcfd_set_diffusion");
@@ -581,6 +611,34 @@ class Eigen {
   Scalar w0_, eps_;
 };
 }  // namespace weno
+
+// limiter/reconstruct.hpp:21-54 on the part's context
+template <typename Part, typename Limiter>
+void Reconstruct(Part *part_ptr, Limiter *limiter_ptr) {
+  mcfd_ctx *ctx = part_ptr->context_;
+  if (!ctx) throw std::runtime_error("mini::limiter::Reconstruct: no spatial object has been built on this part");
+  if constexpr (Limiter::kEigen) {
+    b200::Check(mcfd_limiter_weno_eigen(ctx, limiter_ptr->w0(), limiter_ptr->eps(), -1), ctx, "mcfd_limiter_weno_eigen");
+  } else {
+    b200::Check(mcfd_limiter_weno_lazy(ctx, limiter_ptr->w0(), limiter_ptr->eps(), -1), ctx, "mcfd_limiter_weno_lazy");
+  }
+}
+namespace average {
+template <typename Part>
+void Reconstruct(Part *part_ptr) {   // limiter/average.hpp:11-28
+  mcfd_ctx *ctx = part_ptr->context_;
+  if (!ctx) throw std::runtime_error("average::Reconstruct: no spatial object has been built on this part");
+  b200::Check(mcfd_limiter_reconstruct(ctx, 0), ctx, "mcfd_limiter_reconstruct");
+}
+}  // namespace average
+namespace majority {
+template <typename Part>
+void Reconstruct(Part *part_ptr) {   // limiter/majority.hpp:14-42
+  mcfd_ctx *ctx = part_ptr->context_;
+  if (!ctx) throw std::runtime_error("majority::Reconstruct: no spatial object has been built on this part");
+  b200::Check(mcfd_limiter_reconstruct(ctx, 1), ctx, "mcfd_limiter_reconstruct");
+}
+}  // namespace majority
 }  // namespace limiter
 
 namespace spatial {
@@ -625,6 +683,94 @@ class WithLimiter : public ConcreteFiniteElement {
     }
   }
   Limiter *limiter_ptr_;
+};
+
+// spatial/viscosity.hpp:35-632 as a tag with the class-static interface the drivers and WithViscosity use
+// (demo/euler/sourceless.cpp:118-126, 153).  Like the reference's statics, one spatial object per process is
+// served at a time: the context installed last.
+template <typename P, typename R>
+class EnergyBasedViscosity : public R {
+ public:
+  using Base = R;
+  using Part = P;
+  using Scalar = typename R::Scalar;
+  using Viscosity = EnergyBasedViscosity;                   // viscosity.hpp:547
+  using Property = algebra::Vector<Scalar, R::kComponents>;  // viscosity.hpp:54
+  static constexpr int kDiffusion = MCFD_CELL_VISCOSITY_DDG;
+
+  template <class Spatial>
+  static void Initialize(Spatial *spatial_ptr) {   // viscosity.hpp:549-554
+    ctx_ = spatial_ptr->context();
+    n_cells_ = spatial_ptr->part().CountLocalCells() + spatial_ptr->part().CountGhostCells();
+    using D = typename R::Diffusion;
+    b200::Check(mcfd_set_diffusion(ctx_, D::beta_0_, D::beta_1_, 0.0, 1.0), ctx_, "mcfd_set_diffusion");
+    b200::Check(mcfd_build_damping_matrices(ctx_), ctx_, "mcfd_build_damping_matrices");
+    SetTimeScale(1.0);
+  }
+  static Scalar GetTimeScale() { return time_scale_; }                     // viscosity.hpp:221-226
+  static void SetTimeScale(Scalar time_scale) { time_scale_ = time_scale; }
+  static void UpdateProperties() {                                          // viscosity.hpp:556-572
+    b200::Check(mcfd_update_cell_viscosity(ctx_, time_scale_), ctx_, "mcfd_update_cell_viscosity");
+    cache_valid_ = false;
+  }
+  // the ghost cells' values travel with mcfd_viscosity_halo_* where a host moves bytes between parts
+  static void ShareGhostCellProperties() {}
+  static void UpdateGhostCellProperties() {}
+  template <typename Int>
+  static Property const &GetPropertyOnCell(Int i_cell, int /* i_node */) {  // viscosity.hpp:69-72: constant in a cell
+    if (!cache_valid_) {
+      flat_.resize((size_t)n_cells_ * R::kComponents);
+      b200::Check(mcfd_get_cell_viscosity(ctx_, flat_.data()), ctx_, "mcfd_get_cell_viscosity");
+      cache_.resize(n_cells_);
+      for (int64_t c = 0; c < n_cells_; ++c) {
+        for (int k = 0; k < R::kComponents; ++k) cache_[c][k] = flat_[c * R::kComponents + k];
+      }
+      cache_valid_ = true;
+    }
+    return cache_.at(i_cell);
+  }
+  static mcfd_ctx *context() { return ctx_; }
+
+ private:
+  inline static mcfd_ctx *ctx_ = nullptr;
+  inline static int64_t n_cells_ = 0;
+  inline static Scalar time_scale_ = 1.0;
+  inline static bool cache_valid_ = false;
+  inline static std::vector<Scalar> flat_;
+  inline static std::vector<Property> cache_;
+};
+
+// spatial/with_viscosity.hpp:20-73
+template <typename ConcreteFiniteElement>
+class WithViscosity : public ConcreteFiniteElement {
+ public:
+  using Base = ConcreteFiniteElement;
+  using Riemann = typename Base::Riemann;
+  using Scalar = typename Base::Scalar;
+  using Column = typename Base::Column;
+  template <class... Args>
+  WithViscosity(Args &&...args) : Base(std::forward<Args>(args)...) { Riemann::Viscosity::Initialize(this); }
+  void SetSolutionColumn(Column const &column) override {
+    this->Base::SetSolutionColumn(column);
+    Riemann::Viscosity::UpdateProperties();
+  }
+  template <class Callable>
+  void Approximate(Callable &&func) {   // Base::Approximate ends in the virtual SetSolutionColumn above
+    Base::Approximate(std::forward<Callable>(func));
+  }
+  bool FusedUpdate(int order, double t_curr, double dt) override {
+    if (this->part().CountGhostCells() > 0) return false;
+    mcfd_ctx *ctx = this->context();
+    b200::Check(mcfd_rk_begin(ctx, order, t_curr, dt), ctx, "mcfd_rk_begin");
+    for (int stage = 0; stage < order; ++stage) {
+      b200::Check(mcfd_rk_stage_inner(ctx, stage), ctx, "mcfd_rk_stage_inner");
+      b200::Check(mcfd_rk_stage_inter(ctx, stage), ctx, "mcfd_rk_stage_inter");
+      Riemann::Viscosity::UpdateProperties();
+    }
+    return true;
+  }
+  // with_viscosity.hpp:67-71: CFL * min_dt_ of the last UpdateProperties -- what mcfd_time_step returns on such a
+  // context (Base::GetTimeStep)
 };
 
 namespace fr {

@@ -179,8 +179,8 @@ int mcfd_set_diffusion(mcfd_ctx *ctx, double beta_0, double beta_1, double nu, d
  * value for every cell and component (prandtl unused).  mcfd_set_cell_viscosity replaces
  * EnergyBasedViscosity::properties_ (viscosity.hpp:57, 68-71, 564-566): nu [n_local + n_ghost][5], constant inside a
  * cell; a face uses the mean of its two cells (fr/general.hpp:331-335).  The ghost cells' values are the caller's to
- * exchange (viscosity.hpp:163-189).  The rule that CHOOSES the values (UpdateProperties, viscosity.hpp:556-572, with
- * the damping matrices of :299-384) is not part of this library yet. */
+ * exchange (viscosity.hpp:163-189; mcfd_viscosity_halo_* below).  The rule that CHOOSES the values (UpdateProperties,
+ * viscosity.hpp:556-572, with the damping matrices of :299-384) is mcfd_update_cell_viscosity below. */
 int mcfd_set_cell_viscosity(mcfd_ctx *ctx, int64_t n_cells, const double *nu);
 int mcfd_get_cell_viscosity(mcfd_ctx *ctx, double *nu);   /* [n_local + n_ghost][5] */
 

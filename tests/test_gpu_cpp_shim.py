@@ -102,6 +102,56 @@ def test_sod_driver_with_weno_limiter_through_cpp_template_api(tmp_path, eigen):
     assert np.abs(got - ref).max() / np.abs(ref).max() < 1e-11
 
 
+def _sod_viscosity_reference(n_steps):
+    """Sod with WithViscosity<fr::Lobatto<Part, EnergyBasedViscosity<...>>> (the reference's VISCOSITY build)."""
+    m = meshmod.box(50, 2, 3, hi=(5.0, 0.2, 0.3))
+    left = np.array([1.0, 0, 0, 0, 1.0 / 0.4]); right = np.array([0.125, 0, 0, 0, 0.1 / 0.4])
+    dt_max = 0.2 / 200
+    if not refapi.available(2):
+        return None, None
+    r = refapi.Ref(m, degree=2, scheme=refapi.FR_ENERGY_VISCOSITY, riemann=1, viscous=(2.0, 1.0 / 12, 0.0, 1.0))
+    def ic(tag, xyz, t, out, user):
+        v = left if xyz[0] < 2.5 else right
+        for k in range(5):
+            out[k] = v[k]
+    r.approximate(refapi.F_CALLBACK, cb=ic)
+    r.limiter(0)                                  # average::Reconstruct(part), then ...
+    r.set_solution(r.get_solution())              # ... UpdateProperties (through WithViscosity::SetSolutionColumn)
+    r.set_bc(meshmod.XMIN, refapi.SMART, refapi.F_CONST, left)
+    r.set_bc(meshmod.XMAX, refapi.SMART, refapi.F_CONST, right)
+    for tag in (meshmod.YMIN, meshmod.YMAX, meshmod.ZMIN, meshmod.ZMAX):
+        r.set_bc(tag, refapi.WALL)
+    t = 0.0
+    for _ in range(n_steps):
+        dt = r.time_step(dt_max, 3)
+        r.rk_update(3, t, dt, 1)
+        t += dt
+    return r.get_solution(), r.cell_viscosity()
+
+
+def test_sod_driver_with_energy_based_viscosity_through_cpp_template_api(tmp_path):
+    """-DVISCOSITY: ConvectionDiffusion<Riemann, Direct<Isotropic>> inside EnergyBasedViscosity inside fr::Lobatto inside
+    WithViscosity, SetBetaValues / SetTimeScale / average::Reconstruct(part) / Viscosity::UpdateProperties() as
+    demo/euler/sourceless.hpp:82-103 and sourceless.cpp:117-126, 145-153 spell them."""
+    ref, nu = _sod_viscosity_reference(10)
+    if ref is None:
+        pytest.skip("oracle/_ref not shipped")
+    exe = tmp_path / "shock_tube_viscosity"
+    subprocess.check_call(["g++", "-DUSE_HLLC", "-DVISCOSITY", "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "demo", "euler", "shock_tube.cpp"), "-o", str(exe),
+                           "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200",
+                           "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")])
+    out = tmp_path / "column.bin"
+    res = subprocess.run([str(exe), "10", str(out)], capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout + res.stderr
+    got = np.fromfile(out, dtype=np.float64)
+    plain = _sod_reference(1, 10)
+    assert nu.max() > 0 and np.abs(ref - plain).max() > 1e-4      # the viscosity is on next to the jump
+    assert np.abs(got - ref).max() / np.abs(ref).max() < 1e-11
+    line = [l for l in res.stdout.splitlines() if l.startswith("max cell viscosity")][0]
+    assert float(line.split()[-1]) == pytest.approx(nu.max(), rel=1e-9)
+
+
 def _sod_dgfem_reference(n_steps, limiter=False):
     """Sod with dg::General on the modal polynomial (the reference's DGFEM build, optionally + LIMITER), HLLC."""
     m = meshmod.box(50, 2, 3, hi=(5.0, 0.2, 0.3))
