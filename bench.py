@@ -57,6 +57,9 @@ def parse():
     ap.add_argument("--energy-viscosity", action="store_true",
                     help="WithViscosity<.., EnergyBasedViscosity>: artificial viscosity updated after every stage "
                          "(not the headline workload; single GPU)")
+    ap.add_argument("--frame-output", action="store_true",
+                    help="also time the frame output's sampling step (mcfd_sample_vtk: values at the 27 points of every "
+                         "cell's VTK hexahedron, copied to the host), next to the reference's vtk::Writer::Prepare on the CPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of replaying a CUDA graph")
@@ -430,6 +433,8 @@ def ours(args):
                 "host_issue_ms_per_step": host_issue_ms / args.steps}
         if e2e is not None:
             line["e2e"] = e2e
+        if args.frame_output:
+            line["frame_output"] = frame_output(sp, args)
         if world == 1 and not args.no_cpu_baseline:
             res = cpu_run(args, steps=3, warmup=1)
             line["cpu_baseline"] = {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")}
@@ -438,6 +443,33 @@ def ours(args):
         comm.drain()
         torch.cuda.synchronize()
         dist.destroy_process_group()
+
+
+def frame_output(sp, args):
+    """The step after the path: one frame's sampling through the C ABI, device state -> host arrays."""
+    sp.ctx.sample_vtk(False, points=True)
+    t0 = time.perf_counter()
+    n_frames = 5
+    for _ in range(n_frames):
+        sp.ctx.sample_vtk(False, points=False)
+    ms = 1e3 * (time.perf_counter() - t0) / n_frames
+    n_cells = sp.ctx.n_local
+    out = {"what": "mcfd_sample_vtk (kernel + D2H into pageable memory), values only", "ms_per_frame": ms,
+           "cells_per_s": n_cells / (ms * 1e-3), "d2h_bytes_per_frame": n_cells * 27 * 5 * 8}
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import refapi
+    from minicfd_b200 import mesh as meshmod
+    if refapi.available(args.degree):
+        n = 16
+        m = meshmod.box(n, n, n, hi=(10.0, 10.0, 10.0))
+        r = refapi.Ref(m, degree=args.degree, scheme=refapi.FR, riemann=1)
+        r.approximate(refapi.F_SMOOTH, [1.0])
+        t0 = time.perf_counter()
+        r.sample_vtk()
+        dt = time.perf_counter() - t0
+        out["cpu_reference"] = {"cells_per_s": n ** 3 / dt, "cores": 1, "kind": "reference",
+                                "sample": f"vtk::Writer::Prepare's loop over {n}^3 cells"}
+    return out
 
 
 def main():

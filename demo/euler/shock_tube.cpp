@@ -86,6 +86,8 @@ using Spatial = mini::spatial::WithViscosity<General>;
 #else
 using Spatial = Unlimited;
 #endif
+#include "mini/mesh/vtk.hpp"
+using VtkWriter = mini::mesh::vtk::Writer<Part>;   // demo/euler/sourceless.cpp:38
 #include "mini/temporal/rk.hpp"
 constexpr int kOrders = 3;
 using Temporal = mini::temporal::RungeKutta<kOrders, Scalar>;
@@ -123,9 +125,12 @@ static void BuildBox(Part *part, int nx, int ny, int nz, double lx, double ly, d
 int main(int argc, char *argv[]) {
   int n_steps = argc > 1 ? std::atoi(argv[1]) : 20;
   const char *out_name = argc > 2 ? argv[2] : nullptr;
+  const char *frame_dir = argc > 3 ? argv[3] : nullptr;   // where Frame0 / Frame<n_steps> go (.pvtu + .vtu)
   // input/shock_tube.geo:4-31: [0,5] x [0,0.2] x [0,0.3], h = 0.1
   Part part(0, 1);
   BuildBox(&part, 50, 2, 3, 5.0, 0.2, 0.3);
+  part.SetFieldNames({"Density", "MomentumX", "MomentumY", "MomentumZ", "EnergyStagnationDensity"});   // sourceless.cpp:109-110
+  if (frame_dir) part.SetDirectoryName(frame_dir);
 #ifdef LIMITER   // demo/euler/sourceless.cpp:114-120
   auto limiter = Limiter(/* w0 = */0.001, /* eps = */1e-6);
   Spatial spatial(&limiter, &part);
@@ -139,6 +144,10 @@ int main(int argc, char *argv[]) {
   Diffusion::SetBetaValues(/* ddg_beta_0 = */2.0, /* ddg_beta_1 = */1.0 / 12);
   Spatial spatial(&part);
   RiemannWithViscosity::SetTimeScale(/* time_scale = */1.0);
+  for (int k = 0; k < kComponents; ++k) {   // sourceless.cpp:122-126
+    VtkWriter::AddCellData("CellViscosity" + std::to_string(k + 1),
+        [k](Cell const &cell) { return RiemannWithViscosity::GetPropertyOnCell(cell.id(), 0)[k]; });
+  }
 #else
   Spatial spatial(&part);
 #endif
@@ -156,6 +165,7 @@ int main(int argc, char *argv[]) {
   spatial.SetSmartBoundary("Left", GivenLeft);
   spatial.SetSmartBoundary("Right", GivenRight);
   for (auto name : {"Top", "Bottom", "Front", "Back"}) spatial.SetInviscidWall(name);
+  if (frame_dir) VtkWriter::WriteSolutions(part, "Frame0");   // sourceless.cpp:161-162
   Temporal temporal;
   double t = 0, t_stop = 0.2, dt_max = t_stop / 200;   // sourceless.cpp:68-74 with 10 frames x 20 steps
   for (int i = 0; i < n_steps; ++i) {                  // sourceless.cpp:187-215
@@ -163,6 +173,7 @@ int main(int argc, char *argv[]) {
     temporal.Update(&spatial, t, dt);
     t += dt;
   }
+  if (frame_dir) VtkWriter::WriteSolutions(part, "Frame" + std::to_string(n_steps));   // sourceless.cpp:219-221
   auto column = spatial.GetSolutionColumn();
   double l1[5] = {0, 0, 0, 0, 0};
   for (size_t i = 0; i < column.size(); ++i) l1[i % 5] += std::abs(column[i]);

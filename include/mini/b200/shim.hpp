@@ -21,6 +21,8 @@
 #include <array>
 #include <cmath>
 #include <cstdint>
+#include <fstream>
+#include <sys/stat.h>
 #include <functional>
 #include <map>
 #include <stdexcept>
@@ -264,9 +266,13 @@ class Part {
   static constexpr int kDegrees = Poly::P;
   static constexpr int kComponents = Poly::K;
   static constexpr int kFields = Poly::kFields;
-  struct Cell {   // only what drivers name: `mini::limiter::weno::Lazy<Cell>` (demo/euler/sourceless.hpp:78)
-    using Polynomial = Poly;
+  struct Cell {   // only what drivers name: `mini::limiter::weno::Lazy<Cell>` (demo/euler/sourceless.hpp:78) and the
+    using Polynomial = Poly;   // id a cell-data callback of the VTK writer asks for (sourceless.cpp:122-126)
     using Scalar = typename Poly::Scalar;
+    using Global = typename Poly::Global;
+    using Value = typename Poly::Value;
+    Int id() const { return id_; }
+    Int id_ = -1;
   };
   struct Face {};  // named by the lambda handed to weno::Eigen::InstallRiemannSolvers (demo/euler/rotorcraft.cpp:93-96)
 
@@ -291,6 +297,18 @@ class Part {
   }
   int mpi_rank() const { return rank_; }
   int mpi_size() const { return size_; }
+  // part.hpp:477-485, 1565-1579 (what the VTK writer asks of a part); the reference takes the directory from the
+  // case name in its constructor
+  void SetFieldNames(std::vector<std::string> names) { field_names_ = std::move(names); }
+  const std::string &GetFieldName(int i) const { return field_names_.at(i); }
+  void SetDirectoryName(std::string directory) { directory_ = std::move(directory); }
+  const std::string &GetDirectoryName() const { return directory_; }
+  std::ofstream GetFileStream(std::string const &soln_name, bool binary, std::string const &suffix) const {
+    ::mkdir(directory_.c_str(), 0777);   // the reference runs `mkdir -p` (part.hpp:1568-1573)
+    ::mkdir((directory_ + "/" + soln_name).c_str(), 0777);
+    return std::ofstream(directory_ + "/" + soln_name + "/" + std::to_string(rank_) + "." + suffix,
+        std::ios::out | (binary ? (std::ios::binary) : std::ios::out));
+  }
   Int CountLocalCells() const { return n_local_; }                     // part.hpp:651-658
   Int CountGhostCells() const { return n_ghost_; }
   Int GetCellDataOffset(Int i_cell) const { return i_cell * kFields; }  // part.hpp:784-787
@@ -322,6 +340,8 @@ class Part {
   std::unordered_map<std::string, int32_t> name_to_tag_;
   Halo halo_;
   Int n_local_ = 0, n_ghost_ = 0;
+  std::string directory_ = ".";
+  std::vector<std::string> field_names_;
   // the context of the spatial object built on this part: what `mini::limiter::Reconstruct(&part, ...)` and the
   // like, which the reference hands a Part, act on
   mcfd_ctx *context_ = nullptr;

@@ -285,6 +285,18 @@ int mcfd_time_step_static(int32_t scheme, int32_t degree, int64_t n_cells, const
                           const double *length_dev, double dt_guess, int32_t rk_order, double *dt_dev,
                           void *cuda_stream);
 
+/* Frame output, the step after the path: what mini::mesh::vtk::Writer<Part>::Prepare (include/mini/mesh/vtk.hpp:421-494)
+ * collects for WriteSolutions (:526-668).  Every local hexahedron becomes one VTK tri-quadratic hexahedron (type 29,
+ * vtk.hpp:400-409) of 27 points in VTK's order (vtk.hpp:305-325); points [n_local][27][3] are
+ * coordinate().LocalToGlobal(local), values [n_local][27][5] the current solution at those local coordinates:
+ * modal == 0: Hexahedron::LocalToValue (polynomial/hexahedron.hpp:256-264; on kLocal contexts the interpolated
+ * det(J) u divided by det J at the point); modal != 0: through the L2 projection on the cell's orthonormal basis, as
+ * Extrapolation<Hexahedron> and Projection evaluate it (extrapolation.hpp:180-183, projection.hpp:128-132;
+ * MCFD_DG_GENERAL contexts always).  Either pointer may be null (the points do not change between frames).  The
+ * values are sampled by one kernel over the device-resident state; formatting the .vtu/.pvtu text is the host's job
+ * (include/mini/mesh/vtk.hpp of this repository, minicfd_b200/vtk.py). */
+int mcfd_sample_vtk(mcfd_ctx *ctx, int32_t modal, double *points, double *values);
+
 /* Initial-condition clean-up on the current solution of the local cells: kind 0 =
  * mini::limiter::average::Reconstruct (include/mini/limiter/average.hpp:11-28), kind 1 =
  * mini::limiter::majority::Reconstruct (include/mini/limiter/majority.hpp:14-42), as called by

@@ -64,6 +64,7 @@ SYMBOLS = {
     "mcfd_update_cell_viscosity": (C.c_int, [_P, C.c_double]),
     "mcfd_get_quadrature_points": (C.c_int, [_P, _D]),
     "mcfd_get_jacobian_determinants": (C.c_int, [_P, _D]),
+    "mcfd_sample_vtk": (C.c_int, [_P, C.c_int32, _D, _D]),
     "mcfd_project": (C.c_int, [_P, _D]),
     "mcfd_set_time_callback": (C.c_int, [_P, TIME_CALLBACK, _P]),
     "mcfd_count_local_cells": (C.c_int64, [_P]),
@@ -201,6 +202,13 @@ class Context:
         out = np.empty((self.n_local, self.q ** 3))
         self._check(self.lib.mcfd_get_jacobian_determinants(self.h, _dp(out)))
         return out
+
+    def sample_vtk(self, modal=False, points=True):
+        """mcfd_sample_vtk: (points [n_local][27][3] or None, values [n_local][27][5])"""
+        pts = np.empty((self.n_local, 27, 3)) if points else None
+        values = np.empty((self.n_local, 27, 5))
+        self._check(self.lib.mcfd_sample_vtk(self.h, 1 if modal else 0, _dp(pts) if points else None, _dp(values)))
+        return pts, values
 
     def quadrature_points(self):
         out = np.empty((self.n_local, self.q ** 3, 3))

@@ -2048,6 +2048,80 @@ __global__ void ViscosityHaloKernel(double *nu, double *buffer, const int *cells
   else buffer[i] = *at;
 }
 
+// ---- frame output: mini::mesh::vtk::Writer<Part>::Prepare (mesh/vtk.hpp:421-494) ------------------------------
+// Every hexahedral cell becomes one VTK tri-quadratic hexahedron (vtk.hpp:400-409) whose 27 points carry the
+// solution evaluated at their local coordinates -1/0/+1 (VTK's node order, vtk.hpp:305-325: corners, edges,
+// faces, centre).  values[cell][point][component], the reference's memory order of its `values` vector.
+//   nodal:  Hexahedron::LocalToValue (polynomial/hexahedron.hpp:256-264): sum_k coeff_k phi_k(local), for
+//           kLocal == true divided by det J at the point (the coefficients are det(J_k) u_k there);
+//   modal:  Projection::LocalToGlobalAndValue (projection.hpp:128-132; Extrapolation forwards to its projection,
+//           extrapolation.hpp:180-183): the Taylor form at LocalToGlobal(local) - centre.
+struct VtkSampleArgs {
+  const double *u, *geom, *tay;   // tay: Taylor coefficients, row (mode * mode_stride + comp * comp_stride)
+  double *values;
+  int n_local, modal, k_local, comp_stride, mode_stride;
+  double lag[3][4];               // Lagrange basis on the Q solution nodes evaluated at -1, 0, +1
+};
+__constant__ signed char kVtkHex27[27][3] = {
+  {-1, -1, -1}, {1, -1, -1}, {1, 1, -1}, {-1, 1, -1}, {-1, -1, 1}, {1, -1, 1}, {1, 1, 1}, {-1, 1, 1},
+  {0, -1, -1}, {1, 0, -1}, {0, 1, -1}, {-1, 0, -1}, {0, -1, 1}, {1, 0, 1}, {0, 1, 1}, {-1, 0, 1},
+  {-1, -1, 0}, {1, -1, 0}, {1, 1, 0}, {-1, 1, 0},
+  {-1, 0, 0}, {1, 0, 0}, {0, -1, 0}, {0, 1, 0}, {0, 0, -1}, {0, 0, 1}, {0, 0, 0}};
+
+template <int Q>
+__global__ void __launch_bounds__(256) VtkSampleKernel(VtkSampleArgs p) {
+  constexpr int P = Q - 1, N = Q * Q * Q, F = 5 * N, M = ModalShape<P>::M, kRow = 27 * 5;
+  __shared__ double sOut[kTile * kRow];
+  const int tile = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cell = tile * kTile + lane;
+  const double *geo = p.geom + (size_t)tile * kGeomRows * kTile + lane;
+  if (cell < p.n_local) {
+    for (int pt = warp; pt < 27; pt += 8) {
+      const int a = kVtkHex27[pt][0], b = kVtkHex27[pt][1], c = kVtkHex27[pt][2];
+      double v[5] = {0, 0, 0, 0, 0};
+      if (p.modal) {
+        double d[3], t[M];
+        DgmPoint(geo, kTile, (double)a, (double)b, (double)c, d);
+        TaylorValues<P>(d, t);
+        const double *src = p.tay + (size_t)tile * 5 * M * kTile + lane;
+        for (int j = 0; j < M; ++j) {
+#pragma unroll
+          for (int k = 0; k < 5; ++k) v[k] = fma(src[(size_t)(j * p.mode_stride + k * p.comp_stride) * kTile], t[j], v[k]);
+        }
+      } else {
+        const double *src = p.u + (size_t)tile * F * kTile + lane;
+        for (int i = 0; i < Q; ++i) {
+          const double wi = p.lag[a + 1][i];
+          if (wi == 0) continue;
+          for (int j = 0; j < Q; ++j) {
+            const double wj = wi * p.lag[b + 1][j];
+            if (wj == 0) continue;
+            for (int k = 0; k < Q; ++k) {
+              double w = wj * p.lag[c + 1][k];
+              if (w == 0) continue;
+              if (p.k_local) w *= ComputeMetric(geo, kTile, c_tab.xi[i], c_tab.xi[j], c_tab.xi[k]).det;
+              const int n = (i * Q + j) * Q + k;
+#pragma unroll
+              for (int m = 0; m < 5; ++m) v[m] = fma(w, src[(n * 5 + m) * kTile], v[m]);
+            }
+          }
+        }
+        if (p.k_local) {
+          const double inv = 1.0 / ComputeMetric(geo, kTile, (double)a, (double)b, (double)c).det;
+#pragma unroll
+          for (int m = 0; m < 5; ++m) v[m] *= inv;
+        }
+      }
+#pragma unroll
+      for (int m = 0; m < 5; ++m) sOut[lane * kRow + pt * 5 + m] = v[m];
+    }
+  }
+  __syncthreads();
+  const int valid = min(kTile, p.n_local - tile * kTile) * kRow;   // the tile's rows are contiguous in the output
+  double *dst = p.values + (size_t)tile * kTile * kRow;
+  for (int i = threadIdx.x; i < valid; i += 256) dst[i] = sOut[i];
+}
+
 // Test hook: n independent rotated Riemann problems.
 template <int kRiemann>
 __global__ void RiemannKernel(int bc_kind, int n, const double *normals, const double *ul,

@@ -54,6 +54,7 @@ struct mcfd_ctx {
   DevBuf<double> u[3], res, geom, bvals, length, column;
   DevBuf<double> grad, hn, h2s;                 // viscous traces (TraceKernel) and HolderToSharer vectors
   DevBuf<double> cell_nu;                       // MCFD_CELL_VISCOSITY_DDG: [tile][comp][lane]
+  DevBuf<double> vtk_values;                    // mcfd_sample_vtk: [cell][27][5]
   DevBuf<double> damping;                       // EnergyBasedViscosity: [tile][r*N + c][lane] damping matrices
   DevBuf<unsigned long long> visc_dt_bits;      // min_dt_ of the last mcfd_update_cell_viscosity
   bool energy_viscosity = false;                // WithViscosity mode: the time step comes from min_dt_
@@ -486,7 +487,7 @@ int mcfd_set_mesh(mcfd_ctx *ctx, int64_t n_nodes, const double *xyz, int64_t n_l
     MCFD_CUDA(ctx, ctx->h2s.Alloc(h2s.size()));
     MCFD_CUDA(ctx, cudaMemcpy(ctx->h2s.p, h2s.data(), h2s.size() * sizeof(double), cudaMemcpyHostToDevice));
   }
-  ctx->bas.Free(); ctx->tay.Free(); ctx->frames.Free(); ctx->weno_scratch.Free(); ctx->damping.Free(); ctx->energy_viscosity = false;
+  ctx->bas.Free(); ctx->tay.Free(); ctx->frames.Free(); ctx->weno_scratch.Free(); ctx->damping.Free(); ctx->vtk_values.Free(); ctx->energy_viscosity = false;
   if (ctx->cfg.scheme == MCFD_DG_GENERAL) {   // Projection's orthonormal bases on the Gauss-Legendre rule
     const int rows = ctx->q == 3 ? ModalShape<2>::kBasRows : ModalShape<3>::kBasRows;
     auto bas = ToTiles(ctx->mesh.BuildModalBases(ctx->cfg.degree, true), rows, ctx->n_cells, ctx->n_tiles);
@@ -1171,6 +1172,22 @@ int mcfd_eigen_matrices(mcfd_ctx *ctx, int64_t n, const double *conservative, co
   return MCFD_OK;
 }
 
+// Extrapolation<Hexahedron> on a nodal context: per-cell orthonormal bases, built on the host at first use like the
+// reference does at set-up, and the modal / Taylor coefficient tables
+static int EnsureExtrapolation(mcfd_ctx *ctx) {
+  if (ctx->bas.p) return MCFD_OK;
+  const int m = ctx->q == 3 ? 10 : 20, rows = ctx->q == 3 ? ModalShape<2>::kBasRows : ModalShape<3>::kBasRows;
+  auto bas = ToTiles(ctx->mesh.BuildModalBases(ctx->cfg.degree), rows, ctx->n_cells, ctx->n_tiles);
+  MCFD_CUDA(ctx, ctx->bas.Alloc(bas.size()));
+  MCFD_CUDA(ctx, cudaMemcpy(ctx->bas.p, bas.data(), bas.size() * sizeof(double), cudaMemcpyHostToDevice));
+  const size_t n = (size_t)ctx->n_tiles * 5 * m * kTile;
+  for (DevBuf<double> *b : {&ctx->mod, &ctx->tay, &ctx->mod_new, &ctx->tay_new}) {
+    MCFD_CUDA(ctx, b->Alloc(n));
+    MCFD_CUDA(ctx, cudaMemset(b->p, 0, n * sizeof(double)));
+  }
+  return MCFD_OK;
+}
+
 static int LimiterWeno(mcfd_ctx *ctx, double w0, double eps, int phase, bool eigen) {
   if (int s = RequireMesh(ctx)) return s;
   if (ctx->cfg.k_local) return Fail(ctx, MCFD_ERR_STATE, "the limiters are built for kLocal == false");
@@ -1192,17 +1209,7 @@ static int LimiterWeno(mcfd_ctx *ctx, double w0, double eps, int phase, bool eig
     return MCFD_OK;
   }
   if (phase < -1 || phase > 1) return Fail(ctx, MCFD_ERR_ARG, "phase must be -1 (both), 0 (inner cells) or 1 (inter cells)");
-  const int m = ctx->q == 3 ? 10 : 20, rows = ctx->q == 3 ? ModalShape<2>::kBasRows : ModalShape<3>::kBasRows;
-  if (!ctx->bas.p) {   // first use: per-cell orthonormal bases, built on the host like the reference does at set-up
-    auto bas = ToTiles(ctx->mesh.BuildModalBases(ctx->cfg.degree), rows, ctx->n_cells, ctx->n_tiles);
-    MCFD_CUDA(ctx, ctx->bas.Alloc(bas.size()));
-    MCFD_CUDA(ctx, cudaMemcpy(ctx->bas.p, bas.data(), bas.size() * sizeof(double), cudaMemcpyHostToDevice));
-    const size_t n = (size_t)ctx->n_tiles * 5 * m * kTile;
-    for (DevBuf<double> *b : {&ctx->mod, &ctx->tay, &ctx->mod_new, &ctx->tay_new}) {
-      MCFD_CUDA(ctx, b->Alloc(n));
-      MCFD_CUDA(ctx, cudaMemset(b->p, 0, n * sizeof(double)));
-    }
-  }
+  if (int s = EnsureExtrapolation(ctx)) return s;
   if (eigen && !ctx->frames.p) {
     auto frames = ToTiles(ctx->mesh.frames, 54, ctx->n_cells, ctx->n_tiles);
     MCFD_CUDA(ctx, ctx->frames.Alloc(frames.size()));
@@ -1222,6 +1229,66 @@ static int LimiterWeno(mcfd_ctx *ctx, double w0, double eps, int phase, bool eig
   if (phase != 0) {   // act(inter cells) after UpdateGhostCellCoeffs (limiter/reconstruct.hpp:49-51)
     if (int s = batch(nl, nc, fi, nl, false)) return s;
   }
+  return MCFD_OK;
+}
+
+int mcfd_sample_vtk(mcfd_ctx *ctx, int32_t modal, double *points, double *values) {
+  if (int s = RequireMesh(ctx)) return s;
+  const int64_t nl = ctx->mesh.n_local;
+  static const int vtk[27][3] = {
+    {-1, -1, -1}, {1, -1, -1}, {1, 1, -1}, {-1, 1, -1}, {-1, -1, 1}, {1, -1, 1}, {1, 1, 1}, {-1, 1, 1},
+    {0, -1, -1}, {1, 0, -1}, {0, 1, -1}, {-1, 0, -1}, {0, -1, 1}, {1, 0, 1}, {0, 1, 1}, {-1, 0, 1},
+    {-1, -1, 0}, {1, -1, 0}, {1, 1, 0}, {-1, 1, 0},
+    {-1, 0, 0}, {1, 0, 0}, {0, -1, 0}, {0, 1, 0}, {0, 0, -1}, {0, 0, 1}, {0, 0, 0}};
+  if (points) {   // coordinate().LocalToGlobal(local): static geometry, from the host copy of the trilinear maps
+    for (int64_t c = 0; c < nl; ++c) {
+      const double *g = &ctx->mesh.coef[c * kGeomRows], *o = &ctx->mesh.c0[c * 3];
+      for (int p = 0; p < 27; ++p) {
+        const double x = vtk[p][0], e = vtk[p][1], z = vtk[p][2];
+        for (int k = 0; k < 3; ++k) {
+          points[(c * 27 + p) * 3 + k] = o[k] + g[0 + k] * x + g[3 + k] * e + g[6 + k] * z + g[9 + k] * x * e
+              + g[12 + k] * e * z + g[15 + k] * z * x + g[18 + k] * x * e * z;
+        }
+      }
+    }
+  }
+  if (!values || nl == 0) return MCFD_OK;
+  const bool dgm = ctx->cfg.scheme == MCFD_DG_GENERAL;
+  if (dgm) modal = 1;
+  if (modal && ctx->cfg.k_local) return Fail(ctx, MCFD_ERR_STATE, "the modal polynomials are built for kLocal == false");
+  double *u = HaloState(ctx);
+  VtkSampleArgs a{};
+  a.u = u; a.geom = ctx->geom.p; a.n_local = (int)nl; a.modal = modal ? 1 : 0; a.k_local = ctx->cfg.k_local;
+  const int q = ctx->q, m = q == 3 ? 10 : 20;
+  if (dgm) {   // Projection: the state is the modal coefficients
+    if (int s = LaunchDgmTaylor(ctx, u, 0, nl)) return s;
+    a.tay = ctx->tay.p; a.comp_stride = 1; a.mode_stride = 5;
+  } else if (modal) {   // Extrapolation: UpdateModalCoeff of the current nodal values first
+    if (int s = EnsureExtrapolation(ctx)) return s;
+    const int st = q == 3 ? WenoLazyBatch<3>(ctx, u, 0, 0, 0, nl, 0, 0, false, false)
+                          : WenoLazyBatch<4>(ctx, u, 0, 0, 0, nl, 0, 0, false, false);
+    if (st) return st;
+    a.tay = ctx->tay.p; a.comp_stride = m; a.mode_stride = 1;
+  }
+  for (int r = 0; r < 3; ++r) {   // Lagrange basis on the solution nodes at -1, 0, +1 (basis/lagrange.hpp)
+    const double x = r - 1;
+    for (int i = 0; i < q; ++i) {
+      double v = 1;
+      for (int j = 0; j < q; ++j) if (j != i) v *= (x - ctx->tables.xi[j]) / (ctx->tables.xi[i] - ctx->tables.xi[j]);
+      a.lag[r][i] = v;
+    }
+  }
+  const size_t n = (size_t)nl * 27 * 5;
+  if (ctx->vtk_values.n < n) MCFD_CUDA(ctx, ctx->vtk_values.Alloc(n));
+  a.values = ctx->vtk_values.p;
+  MCFD_CUDA(ctx, EnsureTables(ctx));
+  const int tiles = (int)((nl + kTile - 1) / kTile);
+  if (q == 3) VtkSampleKernel<3><<<tiles, 256, 0, ctx->stream>>>(a);
+  else VtkSampleKernel<4><<<tiles, 256, 0, ctx->stream>>>(a);
+  MCFD_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  MCFD_CUDA(ctx, cudaMemcpyAsync(values, ctx->vtk_values.p, n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return MCFD_OK;
 }
 

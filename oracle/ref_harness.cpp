@@ -30,6 +30,8 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <fstream>
+#include <sys/stat.h>
 #include <functional>
 #include <map>
 #include <memory>
@@ -75,6 +77,7 @@ typedef ompi_request_t *MPI_Request;
 #include "mini/spatial/dg/lobatto.hpp"
 #include "mini/spatial/fr/lobatto.hpp"
 #include "mini/temporal/rk.hpp"
+#include "mini/mesh/vtk.hpp"
 
 #ifndef REF_DEGREE
 #define REF_DEGREE 2
@@ -435,6 +438,17 @@ class OraclePart {
 
   int mpi_rank() const { return rank_; }
   int mpi_size() const { return size_; }
+  // what vtk::Writer<Part>::WriteSolutions asks of a part (part.hpp:477-485, 1565-1579), minus the MPI barrier
+  std::string directory_ = ".";
+  std::vector<std::string> field_names_{"Density", "MomentumX", "MomentumY", "MomentumZ", "EnergyStagnationDensity"};
+  const std::string &GetFieldName(int i) const { return field_names_.at(i); }
+  const std::string &GetDirectoryName() const { return directory_; }
+  std::ofstream GetFileStream(std::string const &soln_name, bool binary, std::string const &suffix) const {
+    ::mkdir(directory_.c_str(), 0777);   // the reference runs `mkdir -p` (part.hpp:1568-1573)
+    ::mkdir((directory_ + "/" + soln_name).c_str(), 0777);
+    return std::ofstream(directory_ + "/" + soln_name + "/" + std::to_string(rank_) + "." + suffix,
+        std::ios::out | (binary ? (std::ios::binary) : std::ios::out));
+  }
   Int CountLocalCells() const { return local_cells_.size(); }
   Int CountGhostCells() const { return ghost_cells_.size(); }
   Int GetCellDataOffset(Int i_cell) const { return i_cell * kFields; }
@@ -599,6 +613,8 @@ struct SolverBase {
   virtual double time_step(double dt_guess, int rk_order) const = 0;
   virtual void cell_geometry(int r, double *length, double *volume) const = 0;
   virtual void limiter(int kind) = 0;
+  virtual void write_vtu(const char *directory, const char *soln_name) = 0;
+  virtual void sample_vtk(int r, double *points, double *values) const = 0;   // [n_local][27][3], [n_local][27][5]
 };
 
 struct NoLimiter { NoLimiter(double, double) {} };
@@ -749,6 +765,40 @@ struct SolverImpl : SolverBase {
       for (auto &p : parts) {
         if (kind == 0) mini::limiter::average::Reconstruct(p.get());
         else mini::limiter::majority::Reconstruct(p.get());
+      }
+    }
+  }
+  // mini::mesh::vtk::Writer<Part>::WriteSolutions(part, soln_name) as demo/euler/sourceless.cpp:161-162, 220-221 calls
+  // it, part after part; with the CellViscosity1..5 cell data of sourceless.cpp:122-126 on the VISCOSITY scheme
+  void write_vtu(const char *directory, const char *soln_name) override {
+    using Writer = mini::mesh::vtk::Writer<Part>;
+    if constexpr (requires { typename Spatial::Riemann::Viscosity; }) {
+      static bool installed = false;
+      if (!installed) {
+        using V = typename Spatial::Riemann::Viscosity;
+        for (int k = 0; k < 5; ++k) {
+          Writer::AddCellData("CellViscosity" + std::to_string(k + 1),
+              [k](typename Part::Cell const &cell) { return V::GetPropertyOnCell(cell.id(), 0)[k]; });
+        }
+        installed = true;
+      }
+    }
+    for (auto &p : parts) {
+      p->directory_ = directory;
+      Writer::WriteSolutions(*p, soln_name);
+    }
+  }
+  // what vtk::Writer<Part>::Prepare (vtk.hpp:421-494) collects per cell, at full precision
+  void sample_vtk(int r, double *points, double *values) const override {
+    using Cell = typename Part::Cell;
+    using Coord = typename Cell::Global;
+    for (Cell const &cell : parts[r]->GetLocalCells()) {
+      for (int i = 0; i < 27; ++i) {
+        Coord global;
+        typename Cell::Value value;
+        cell.polynomial().LocalToGlobalAndValue(mini::mesh::vtk::Hexahedron27<Coord>::locals[i], &global, &value);
+        for (int d = 0; d < 3; ++d) *points++ = global[d];
+        for (int k = 0; k < 5; ++k) *values++ = value[k];
       }
     }
   }
@@ -1016,6 +1066,12 @@ double REF_FN(time_step)(void *h, double dt_guess, int rk_order) {
   return static_cast<SolverBase *>(h)->time_step(dt_guess, rk_order);
 }
 void REF_FN(limiter)(void *h, int kind) { static_cast<SolverBase *>(h)->limiter(kind); }
+void REF_FN(sample_vtk)(void *h, int r, double *points, double *values) {
+  static_cast<SolverBase *>(h)->sample_vtk(r, points, values);
+}
+void REF_FN(write_vtu)(void *h, const char *directory, const char *soln_name) {
+  static_cast<SolverBase *>(h)->write_vtu(directory, soln_name);
+}
 void REF_FN(cell_geometry)(void *h, int r, double *length, double *volume) {
   static_cast<SolverBase *>(h)->cell_geometry(r, length, volume);
 }

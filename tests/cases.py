@@ -164,3 +164,9 @@ DGM_WENO_GOLDEN_CASES = [("dgm_weno_p2_hllc", 2, 1), ("dgm_weno_p3_hllc", 3, 1)]
 # ---- kLocal == true expansions: columns hold det(J) u (demo/laminar/shockless.hpp:66-69; BASELINE config 4) -------
 LOCAL_GOLDEN_CASES = [("local_euler_p2_hllc", 2, 1, False), ("local_ns_p2_hllc", 2, 1, True),
                       ("local_ns_p3_exact", 3, 0, True)]    # (name, degree, riemann, viscous)
+
+# frame output (mini::mesh::vtk::Writer): (name, degree, reference scheme id, what the polynomial is)
+VTK_GOLDEN_CASES = [("vtk_nodal_p2", 2, 0, "nodal"), ("vtk_nodal_p3", 3, 0, "nodal"),
+                    ("vtk_local_p2", 2, 11, "local"), ("vtk_local_p3", 3, 11, "local"),
+                    ("vtk_extrapolation_p2", 2, 4, "extrapolation"), ("vtk_extrapolation_p3", 3, 4, "extrapolation"),
+                    ("vtk_projection_p2", 2, 9, "projection"), ("vtk_projection_p3", 3, 9, "projection")]

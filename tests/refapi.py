@@ -179,6 +179,17 @@ class Ref:
         f = self._f("time_step"); f.restype = C.c_double
         return float(f(self.h, C.c_double(dt_guess), C.c_int(rk_order)))
 
+    def sample_vtk(self, r=0):
+        """What vtk::Writer<Part>::Prepare collects: (points [n_local][27][3], values [n_local][27][5])"""
+        n = self.count_local(r)
+        pts, val = np.empty((n, 27, 3)), np.empty((n, 27, 5))
+        self._f("sample_vtk")(self.h, C.c_int(r), _dp(pts), _dp(val))
+        return pts, val
+
+    def write_vtu(self, directory, soln_name):
+        """mini::mesh::vtk::Writer<Part>::WriteSolutions(part, soln_name) for every part, files under `directory`"""
+        self._f("write_vtu")(self.h, C.c_char_p(str(directory).encode()), C.c_char_p(soln_name.encode()))
+
     def limiter(self, kind):
         self._f("limiter")(self.h, C.c_int(kind))
 

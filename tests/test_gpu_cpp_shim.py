@@ -102,7 +102,7 @@ def test_sod_driver_with_weno_limiter_through_cpp_template_api(tmp_path, eigen):
     assert np.abs(got - ref).max() / np.abs(ref).max() < 1e-11
 
 
-def _sod_viscosity_reference(n_steps):
+def _sod_viscosity_reference(n_steps, frames=None):
     """Sod with WithViscosity<fr::Lobatto<Part, EnergyBasedViscosity<...>>> (the reference's VISCOSITY build)."""
     m = meshmod.box(50, 2, 3, hi=(5.0, 0.2, 0.3))
     left = np.array([1.0, 0, 0, 0, 1.0 / 0.4]); right = np.array([0.125, 0, 0, 0, 0.1 / 0.4])
@@ -121,11 +121,15 @@ def _sod_viscosity_reference(n_steps):
     r.set_bc(meshmod.XMAX, refapi.SMART, refapi.F_CONST, right)
     for tag in (meshmod.YMIN, meshmod.YMAX, meshmod.ZMIN, meshmod.ZMAX):
         r.set_bc(tag, refapi.WALL)
+    if frames:
+        r.write_vtu(frames, "Frame0")
     t = 0.0
     for _ in range(n_steps):
         dt = r.time_step(dt_max, 3)
         r.rk_update(3, t, dt, 1)
         t += dt
+    if frames:
+        r.write_vtu(frames, "Frame%d" % n_steps)
     return r.get_solution(), r.cell_viscosity()
 
 
