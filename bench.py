@@ -446,29 +446,43 @@ def ours(args):
 
 
 def frame_output(sp, args):
-    """The step after the path: one frame's sampling through the C ABI, device state -> host arrays."""
-    sp.ctx.sample_vtk(False, points=True)
+    """The step after the path: one frame written through vtk.Writer -- values sampled and turned into
+    text on the device, bytes written by the host -- next to the reference's vtk::Writer<Part>::WriteSolutions."""
+    import shutil
+    import tempfile
+    from minicfd_b200 import mesh as meshmod, vtk
+    d = tempfile.mkdtemp()
+    w = vtk.Writer(sp)
+    w.WriteSolutions(d, "Frame0")               # first frame: encodes the static points and cell arrays
     t0 = time.perf_counter()
-    n_frames = 5
-    for _ in range(n_frames):
-        sp.ctx.sample_vtk(False, points=False)
+    n_frames = 3
+    for i in range(n_frames):
+        w.WriteSolutions(d, "Frame%d" % (i + 1))
     ms = 1e3 * (time.perf_counter() - t0) / n_frames
+    t0 = time.perf_counter()
+    sp.ctx.sample_vtk_on_device(False)
+    texts = [sp.ctx.vtk_component_text(k) for k in range(5)]
+    ms_text = 1e3 * (time.perf_counter() - t0)
     n_cells = sp.ctx.n_local
-    out = {"what": "mcfd_sample_vtk (kernel + D2H into pageable memory), values only", "ms_per_frame": ms,
-           "cells_per_s": n_cells / (ms * 1e-3), "d2h_bytes_per_frame": n_cells * 27 * 5 * 8}
+    size = os.path.getsize(os.path.join(d, "Frame1", "0.vtu"))
+    shutil.rmtree(d)
+    out = {"what": "vtk.Writer.WriteSolutions: sampling + number formatting on the GPU, file written by the host",
+           "ms_per_frame": ms, "cells_per_s": n_cells / (ms * 1e-3), "file_bytes": size,
+           "ms_sample_and_format_5_fields": ms_text, "text_bytes_5_fields": sum(len(t) for t in texts)}
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import refapi
-    from minicfd_b200 import mesh as meshmod
     if refapi.available(args.degree):
         n = 16
         m = meshmod.box(n, n, n, hi=(10.0, 10.0, 10.0))
         r = refapi.Ref(m, degree=args.degree, scheme=refapi.FR, riemann=1)
         r.approximate(refapi.F_SMOOTH, [1.0])
+        d = tempfile.mkdtemp()
         t0 = time.perf_counter()
-        r.sample_vtk()
+        r.write_vtu(d, "Frame0")
         dt = time.perf_counter() - t0
+        shutil.rmtree(d)
         out["cpu_reference"] = {"cells_per_s": n ** 3 / dt, "cores": 1, "kind": "reference",
-                                "sample": f"vtk::Writer::Prepare's loop over {n}^3 cells"}
+                                "sample": f"vtk::Writer<Part>::WriteSolutions of {n}^3 cells"}
     return out
 
 

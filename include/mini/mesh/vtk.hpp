@@ -64,15 +64,18 @@ class Writer {
     if (!ctx) throw std::runtime_error("vtk::Writer: no spatial object has been built on this part");
     constexpr int K = Part::kComponents, kNodes = 27;
     const size_t n_cells = (size_t)part.CountLocalCells(), n_points = n_cells * kNodes;
-    std::vector<double> coords(n_points * 3), values(n_points * K);
     using Polynomial = typename Part::Polynomial;
     constexpr bool kModal = requires { Polynomial::kModal; } || requires { Polynomial::kModalOnly; };
-    b200::Check(mcfd_sample_vtk(ctx, kModal ? 1 : 0, coords.data(), values.data()), ctx, "mcfd_sample_vtk");
+    // the point values are only brought to the host when a callback wants to see them
+    const bool need_values = !point_data_.empty() || static_cast<bool>(shift_by_value_);
+    std::vector<double> coords(n_points * 3), values(need_values ? n_points * K : 0);
+    b200::Check(mcfd_sample_vtk(ctx, kModal ? 1 : 0, coords.data(), need_values ? values.data() : nullptr), ctx,
+        "mcfd_sample_vtk");
     std::vector<std::vector<Scalar>> point_data(point_data_.size()), cell_data(cell_data_.size());
     for (size_t c = 0; c < n_cells; ++c) {   // Prepare (vtk.hpp:421-494) on the sampled values
       Cell cell;
       cell.id_ = (typename Part::Index)c;
-      for (int i = 0; i < kNodes; ++i) {
+      for (int i = 0; need_values && i < kNodes; ++i) {
         const size_t at = c * kNodes + i;
         Coord global;
         Value value;
@@ -101,40 +104,44 @@ class Writer {
       pvtu << "  </PUnstructuredGrid>\n</VTKFile>\n";
     }
     auto vtu = part.GetFileStream(soln_name, false, "vtu");
+    // every number becomes text on the GPU (`vtu << v << ' '` = "%g "); the host only writes bytes
     std::string text;
-    auto array = [&](std::string const &name, auto &&for_each) {
-      vtu << "        <DataArray type=\"Float64\" Name=\"" << name << "\" format=\"ascii\">\n";
-      text.clear();
-      char buf[32];
-      for_each([&](double v) { text.append(buf, std::snprintf(buf, sizeof buf, "%g ", v)); });   // `vtu << v << ' '`
-      vtu << text << "\n        </DataArray>\n";
+    auto emit = [&](std::string const &type, std::string const &name, int64_t count, auto &&fill) {
+      text.resize((size_t)count * 16 + 16);
+      int64_t length = 0;
+      b200::Check(fill(text.data(), (int64_t)text.size(), &length), ctx, "formatting a DataArray");
+      vtu << "        <DataArray type=\"" << type << "\" Name=\"" << name << "\" format=\"ascii\">\n";
+      vtu.write(text.data(), length);
+      vtu << "\n        </DataArray>\n";
+    };
+    auto array = [&](std::string const &name, std::vector<Scalar> const &data) {
+      emit("Float64", name, (int64_t)data.size(), [&](char *t, int64_t cap, int64_t *len) {
+        return mcfd_format_doubles(ctx, (int64_t)data.size(), data.data(), t, cap, len); });
     };
     vtu << "<VTKFile type=\"UnstructuredGrid\" version=\"1.0\" byte_order=" << endianness << " header_type=\"UInt64\">\n";
     vtu << "  <UnstructuredGrid>\n";
     vtu << "    <Piece NumberOfPoints=\"" << n_points << "\" NumberOfCells=\"" << n_cells << "\">\n";
     vtu << "      <PointData>\n";
     for (int k = 0; k < K; ++k) {
-      array(part.GetFieldName(k), [&](auto &&emit) { for (size_t i = 0; i < n_points; ++i) emit(values[i * K + k]); });
+      emit("Float64", part.GetFieldName(k), (int64_t)n_points, [&](char *t, int64_t cap, int64_t *len) {
+        return mcfd_vtk_component_text(ctx, k, t, cap, len); });
     }
-    for (size_t k = 0; k < point_data_.size(); ++k) {
-      array(point_data_[k].first, [&](auto &&emit) { for (Scalar v : point_data[k]) emit(v); });
-    }
+    for (size_t k = 0; k < point_data_.size(); ++k) array(point_data_[k].first, point_data[k]);
     vtu << "      </PointData>\n      <CellData>\n";
-    for (size_t k = 0; k < cell_data_.size(); ++k) {
-      array(cell_data_[k].first, [&](auto &&emit) { for (Scalar v : cell_data[k]) emit(v); });
-    }
+    for (size_t k = 0; k < cell_data_.size(); ++k) array(cell_data_[k].first, cell_data[k]);
     vtu << "      </CellData>\n      <Points>\n";
     vtu << "        <DataArray type=\"Float64\" Name=\"Points\" NumberOfComponents=\"3\" format=\"binary\">\n";
     const std::uint64_t n_byte = coords.size() * sizeof(double);
     vtu << EncodeBase64(&n_byte, sizeof n_byte) << EncodeBase64(coords.data(), n_byte);
     vtu << "\n        </DataArray>\n      </Points>\n      <Cells>\n";
-    vtu << "        <DataArray type=\"Int32\" Name=\"connectivity\" format=\"ascii\">\n";
-    for (size_t i = 0; i < n_points; ++i) vtu << i << ' ';
-    vtu << "\n        </DataArray>\n        <DataArray type=\"Int32\" Name=\"offsets\" format=\"ascii\">\n";
-    for (size_t c = 0; c < n_cells; ++c) vtu << (c + 1) * kNodes << ' ';
-    vtu << "\n        </DataArray>\n        <DataArray type=\"UInt8\" Name=\"types\" format=\"ascii\">\n";
-    for (size_t c = 0; c < n_cells; ++c) vtu << static_cast<int>(CellType::kHexahedron27) << ' ';
-    vtu << "\n        </DataArray>\n      </Cells>\n    </Piece>\n  </UnstructuredGrid>\n</VTKFile>\n";
+    auto integers = [&](const char *type, const char *name, int64_t count, int64_t first, int64_t step) {
+      emit(type, name, count, [&](char *t, int64_t cap, int64_t *len) {
+        return mcfd_format_integers(ctx, count, first, step, t, cap, len); });
+    };
+    integers("Int32", "connectivity", (int64_t)n_points, 0, 1);
+    integers("Int32", "offsets", (int64_t)n_cells, kNodes, kNodes);
+    integers("UInt8", "types", (int64_t)n_cells, static_cast<int>(CellType::kHexahedron27), 0);
+    vtu << "      </Cells>\n    </Piece>\n  </UnstructuredGrid>\n</VTKFile>\n";
   }
 
  private:

@@ -297,6 +297,22 @@ int mcfd_time_step_static(int32_t scheme, int32_t degree, int64_t n_cells, const
  * (include/mini/mesh/vtk.hpp of this repository, minicfd_b200/vtk.py). */
 int mcfd_sample_vtk(mcfd_ctx *ctx, int32_t modal, double *points, double *values);
 
+/* The text of a frame's arrays, built on the GPU.  WriteSolutions prints every number through `vtu << v << ' '`
+ * (vtk.hpp:600-602, 610-612, 622-624; the stream's default format = printf's "%g", six significant digits correctly
+ * rounded) and the integer arrays through `vtu << i << ' '` (vtk.hpp:650-665); at 10 M numbers per frame that costs the
+ * host far more than the time steps between two frames.  These calls return exactly those characters (no terminating
+ * zero, *length bytes) into text[capacity]; 16 bytes per value always suffice; on MCFD_ERR_ARG for a short buffer
+ * *length holds the size needed.  Values whose sixth digit the device cannot decide (a scaled fraction within 1e-6 of
+ * one half, |v| outside 1e-294..1e+304) are formatted by the host's snprintf inside the call.
+ * mcfd_vtk_component_text: component k of the samples of the last mcfd_sample_vtk (which may be called with
+ * values == NULL to keep them on the device), point after point, cell after cell.
+ * mcfd_format_doubles: n host values (extra point / cell data).  mcfd_format_integers: first + i * step, i < n
+ * (connectivity: 0, 1; offsets: 27, 27; types: 29, 0). */
+int mcfd_vtk_component_text(mcfd_ctx *ctx, int32_t component, char *text, int64_t capacity, int64_t *length);
+int mcfd_format_doubles(mcfd_ctx *ctx, int64_t n, const double *values, char *text, int64_t capacity, int64_t *length);
+int mcfd_format_integers(mcfd_ctx *ctx, int64_t n, int64_t first, int64_t step, char *text, int64_t capacity,
+                         int64_t *length);
+
 /* Initial-condition clean-up on the current solution of the local cells: kind 0 =
  * mini::limiter::average::Reconstruct (include/mini/limiter/average.hpp:11-28), kind 1 =
  * mini::limiter::majority::Reconstruct (include/mini/limiter/majority.hpp:14-42), as called by

@@ -65,6 +65,9 @@ SYMBOLS = {
     "mcfd_get_quadrature_points": (C.c_int, [_P, _D]),
     "mcfd_get_jacobian_determinants": (C.c_int, [_P, _D]),
     "mcfd_sample_vtk": (C.c_int, [_P, C.c_int32, _D, _D]),
+    "mcfd_vtk_component_text": (C.c_int, [_P, C.c_int32, C.c_char_p, C.c_int64, _I64]),
+    "mcfd_format_doubles": (C.c_int, [_P, C.c_int64, _D, C.c_char_p, C.c_int64, _I64]),
+    "mcfd_format_integers": (C.c_int, [_P, C.c_int64, C.c_int64, C.c_int64, C.c_char_p, C.c_int64, _I64]),
     "mcfd_project": (C.c_int, [_P, _D]),
     "mcfd_set_time_callback": (C.c_int, [_P, TIME_CALLBACK, _P]),
     "mcfd_count_local_cells": (C.c_int64, [_P]),
@@ -209,6 +212,27 @@ class Context:
         values = np.empty((self.n_local, 27, 5))
         self._check(self.lib.mcfd_sample_vtk(self.h, 1 if modal else 0, _dp(pts) if points else None, _dp(values)))
         return pts, values
+
+    def sample_vtk_on_device(self, modal=False):
+        """mcfd_sample_vtk with the values kept on the device (for vtk_component_text)."""
+        self._check(self.lib.mcfd_sample_vtk(self.h, 1 if modal else 0, None, None))
+
+    def _text(self, n, call):
+        buf = np.empty(16 * max(int(n), 1), dtype=np.uint8)      # not zero-filled: only `length` bytes get touched
+        length = C.c_int64(0)
+        self._check(call(buf.ctypes.data_as(C.c_char_p), C.c_int64(buf.size), C.byref(length)))
+        return buf[:length.value].data                            # a bytes-like view, no copy
+
+    def vtk_component_text(self, component):
+        """bytes: `vtu << v << ' '` over component k of the last samples (mcfd_vtk_component_text)"""
+        return self._text(self.n_local * 27, lambda b, c, l: self.lib.mcfd_vtk_component_text(self.h, component, b, c, l))
+
+    def format_doubles(self, values):
+        v = np.ascontiguousarray(values, dtype=np.float64).reshape(-1)
+        return self._text(v.size, lambda b, c, l: self.lib.mcfd_format_doubles(self.h, v.size, _dp(v), b, c, l))
+
+    def format_integers(self, n, first, step):
+        return self._text(n, lambda b, c, l: self.lib.mcfd_format_integers(self.h, n, first, step, b, c, l))
 
     def quadrature_points(self):
         out = np.empty((self.n_local, self.q ** 3, 3))

@@ -1,5 +1,6 @@
 // libmcfd.cu — the C ABI of include/minicfd_b200.h on top of kernels.cuh.
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <memory>
@@ -10,6 +11,7 @@
 
 #include "../../include/minicfd_b200.h"
 #include "kernels.cuh"
+#include "format.cuh"
 #include "tables.hpp"
 
 using namespace mcfd;
@@ -55,6 +57,13 @@ struct mcfd_ctx {
   DevBuf<double> grad, hn, h2s;                 // viscous traces (TraceKernel) and HolderToSharer vectors
   DevBuf<double> cell_nu;                       // MCFD_CELL_VISCOSITY_DDG: [tile][comp][lane]
   DevBuf<double> vtk_values;                    // mcfd_sample_vtk: [cell][27][5]
+  // text of the frame's arrays (format.cuh): tokens, their lengths, per-CTA sums and offsets, packed text
+  DevBuf<uint4> fmt_slots;
+  DevBuf<unsigned char> fmt_lens;
+  DevBuf<unsigned int> fmt_sums, fmt_unsure;    // fmt_unsure: [0] = count, then the indices
+  DevBuf<unsigned long long> fmt_offsets;
+  DevBuf<char> fmt_text;
+  DevBuf<double> fmt_pow10, fmt_values;
   DevBuf<double> damping;                       // EnergyBasedViscosity: [tile][r*N + c][lane] damping matrices
   DevBuf<unsigned long long> visc_dt_bits;      // min_dt_ of the last mcfd_update_cell_viscosity
   bool energy_viscosity = false;                // WithViscosity mode: the time step comes from min_dt_
@@ -1252,7 +1261,7 @@ int mcfd_sample_vtk(mcfd_ctx *ctx, int32_t modal, double *points, double *values
       }
     }
   }
-  if (!values || nl == 0) return MCFD_OK;
+  if (nl == 0) return MCFD_OK;
   const bool dgm = ctx->cfg.scheme == MCFD_DG_GENERAL;
   if (dgm) modal = 1;
   if (modal && ctx->cfg.k_local) return Fail(ctx, MCFD_ERR_STATE, "the modal polynomials are built for kLocal == false");
@@ -1287,9 +1296,106 @@ int mcfd_sample_vtk(mcfd_ctx *ctx, int32_t modal, double *points, double *values
   else VtkSampleKernel<4><<<tiles, 256, 0, ctx->stream>>>(a);
   MCFD_CUDA(ctx, cudaGetLastError());
   ctx->launches++;
-  MCFD_CUDA(ctx, cudaMemcpyAsync(values, ctx->vtk_values.p, n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
-  MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (values) {   // null: the samples stay on the device for mcfd_vtk_component_text
+    MCFD_CUDA(ctx, cudaMemcpyAsync(values, ctx->vtk_values.p, n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  }
   return MCFD_OK;
+}
+
+// ---- text of a frame's arrays (format.cuh) -------------------------------------------------------------------------
+static const unsigned int kUnsureCapacity = 1u << 16;
+
+// values_dev[i * stride] (kind 0) or first + i * step (kind 1), i < n, as blank-separated tokens into text[capacity]
+static int FormatAndPack(mcfd_ctx *ctx, int kind, const double *values_dev, int64_t stride, int64_t n, int64_t first,
+    int64_t step, char *text, int64_t capacity, int64_t *length) {
+  if (!text || !length || n < 0) return Fail(ctx, MCFD_ERR_ARG, "null text / length");
+  *length = 0;
+  if (n == 0) return MCFD_OK;
+  if (n > 0x7fffffffll) return Fail(ctx, MCFD_ERR_ARG, "too many values for one array");
+  if (!ctx->fmt_pow10.p) {   // 10^k as a double pair, from the host's long double arithmetic
+    std::vector<double> t(2 * (kPow10Max - kPow10Min + 1));
+    BuildPow10Table(t.data());
+    MCFD_CUDA(ctx, ctx->fmt_pow10.Alloc(t.size()));
+    MCFD_CUDA(ctx, cudaMemcpy(ctx->fmt_pow10.p, t.data(), t.size() * sizeof(double), cudaMemcpyHostToDevice));
+    MCFD_CUDA(ctx, ctx->fmt_unsure.Alloc(1 + kUnsureCapacity));
+  }
+  const int n_blocks = (int)((n + kPackPerBlock - 1) / kPackPerBlock);
+  if (ctx->fmt_slots.n < (size_t)n) {
+    MCFD_CUDA(ctx, ctx->fmt_slots.Alloc(n));
+    MCFD_CUDA(ctx, ctx->fmt_lens.Alloc(n));
+    MCFD_CUDA(ctx, ctx->fmt_text.Alloc((size_t)n * kTokenSlot));
+    MCFD_CUDA(ctx, ctx->fmt_sums.Alloc(n_blocks));
+    MCFD_CUDA(ctx, ctx->fmt_offsets.Alloc(n_blocks + 1));
+  }
+  FormatArgs a{};
+  a.values = values_dev; a.stride = stride; a.n = n; a.first = first; a.step = step; a.kind = kind;
+  a.pow10 = ctx->fmt_pow10.p; a.slots = ctx->fmt_slots.p; a.lens = ctx->fmt_lens.p;
+  a.unsure_count = ctx->fmt_unsure.p; a.unsure_index = ctx->fmt_unsure.p + 1; a.unsure_capacity = kUnsureCapacity;
+  MCFD_CUDA(ctx, cudaMemsetAsync(ctx->fmt_unsure.p, 0, sizeof(unsigned int), ctx->stream));
+  FormatTokensKernel<<<(int)((n + 255) / 256), 256, 0, ctx->stream>>>(a);
+  MCFD_CUDA(ctx, cudaGetLastError());
+  unsigned int n_unsure = 0;
+  MCFD_CUDA(ctx, cudaMemcpyAsync(&n_unsure, ctx->fmt_unsure.p, sizeof n_unsure, cudaMemcpyDeviceToHost, ctx->stream));
+  MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (n_unsure) {   // rounding too close to call on the device, or beyond its table: snprintf decides
+    const bool all = n_unsure > kUnsureCapacity;   // pathological input: the host formats the whole array
+    std::vector<unsigned int> index(all ? 0 : n_unsure);
+    if (!all) MCFD_CUDA(ctx, cudaMemcpy(index.data(), ctx->fmt_unsure.p + 1, n_unsure * sizeof(unsigned int), cudaMemcpyDeviceToHost));
+    std::vector<double> column;
+    if (all) {
+      column.resize((size_t)n);
+      MCFD_CUDA(ctx, cudaMemcpy2D(column.data(), sizeof(double), values_dev, stride * sizeof(double), sizeof(double), n,
+          cudaMemcpyDeviceToHost));
+    }
+    const size_t count = all ? (size_t)n : n_unsure;
+    for (size_t j = 0; j < count; ++j) {
+      const size_t i = all ? j : index[j];
+      double v;
+      if (all) v = column[i];
+      else MCFD_CUDA(ctx, cudaMemcpy(&v, values_dev + i * stride, sizeof v, cudaMemcpyDeviceToHost));
+      char token[32] = {0};
+      const unsigned char len = (unsigned char)std::snprintf(token, sizeof token, "%g ", v);
+      MCFD_CUDA(ctx, cudaMemcpy(ctx->fmt_slots.p + i, token, kTokenSlot, cudaMemcpyHostToDevice));
+      MCFD_CUDA(ctx, cudaMemcpy(ctx->fmt_lens.p + i, &len, 1, cudaMemcpyHostToDevice));
+    }
+  }
+  TokenBlockSumsKernel<<<n_blocks, 256, 0, ctx->stream>>>(ctx->fmt_lens.p, n, ctx->fmt_sums.p);
+  TokenScanKernel<<<1, 1024, 0, ctx->stream>>>(ctx->fmt_sums.p, n_blocks, ctx->fmt_offsets.p);
+  TokenPackKernel<<<n_blocks, 256, 0, ctx->stream>>>(ctx->fmt_slots.p, ctx->fmt_lens.p, n, ctx->fmt_offsets.p, ctx->fmt_text.p);
+  MCFD_CUDA(ctx, cudaGetLastError());
+  ctx->launches += 4;
+  unsigned long long total = 0;
+  MCFD_CUDA(ctx, cudaMemcpyAsync(&total, ctx->fmt_offsets.p + n_blocks, sizeof total, cudaMemcpyDeviceToHost, ctx->stream));
+  MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  *length = (int64_t)total;
+  if ((int64_t)total > capacity) return Fail(ctx, MCFD_ERR_ARG, "text buffer too small (16 bytes per value always suffice)");
+  MCFD_CUDA(ctx, cudaMemcpy(text, ctx->fmt_text.p, total, cudaMemcpyDeviceToHost));
+  return MCFD_OK;
+}
+
+int mcfd_format_doubles(mcfd_ctx *ctx, int64_t n, const double *values, char *text, int64_t capacity, int64_t *length) {
+  if (!ctx) return MCFD_ERR_ARG;
+  if (n > 0 && !values) return Fail(ctx, MCFD_ERR_ARG, "null values");
+  if (n > 0) {
+    if (ctx->fmt_values.n < (size_t)n) MCFD_CUDA(ctx, ctx->fmt_values.Alloc(n));
+    MCFD_CUDA(ctx, cudaMemcpyAsync(ctx->fmt_values.p, values, n * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  }
+  return FormatAndPack(ctx, 0, ctx->fmt_values.p, 1, n, 0, 0, text, capacity, length);
+}
+
+int mcfd_format_integers(mcfd_ctx *ctx, int64_t n, int64_t first, int64_t step, char *text, int64_t capacity,
+    int64_t *length) {
+  if (!ctx) return MCFD_ERR_ARG;
+  return FormatAndPack(ctx, 1, nullptr, 0, n, first, step, text, capacity, length);
+}
+
+int mcfd_vtk_component_text(mcfd_ctx *ctx, int32_t component, char *text, int64_t capacity, int64_t *length) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (component < 0 || component >= 5) return Fail(ctx, MCFD_ERR_ARG, "component must be 0..4");
+  const int64_t n = ctx->mesh.n_local * 27;
+  if (ctx->vtk_values.n < (size_t)n * 5) return Fail(ctx, MCFD_ERR_STATE, "call mcfd_sample_vtk first");
+  return FormatAndPack(ctx, 0, ctx->vtk_values.p + component, 5, n, 0, 0, text, capacity, length);
 }
 
 int64_t mcfd_launch_count(const mcfd_ctx *ctx) { return ctx ? ctx->launches : 0; }

@@ -46,36 +46,40 @@ def write_pvtu(directory, soln_name, n_parts, field_names=FIELD_NAMES, point_dat
         f.write("\n".join(lines))
 
 
+def _assemble(path, n_cells, fields, point_data, cell_data, points_block, connectivity, offsets, types):
+    """vtk.hpp:574-667 from ready-made array bodies (bytes): fields / point_data / cell_data = [(name, body)]."""
+    n_points = n_cells * 27
+    out = [b'<VTKFile type="UnstructuredGrid" version="1.0" byte_order="LittleEndian" header_type="UInt64">',
+           b"  <UnstructuredGrid>", b'    <Piece NumberOfPoints="%d" NumberOfCells="%d">' % (n_points, n_cells),
+           b"      <PointData>"]
+    for name, body in list(fields) + list(point_data):
+        out += [b'        <DataArray type="Float64" Name="%s" format="ascii">' % name.encode(), body, b"        </DataArray>"]
+    out += [b"      </PointData>", b"      <CellData>"]
+    for name, body in cell_data:
+        out += [b'        <DataArray type="Float64" Name="%s" format="ascii">' % name.encode(), body, b"        </DataArray>"]
+    out += [b"      </CellData>", b"      <Points>",
+            b'        <DataArray type="Float64" Name="Points" NumberOfComponents="3" format="binary">',
+            points_block, b"        </DataArray>", b"      </Points>", b"      <Cells>",
+            b'        <DataArray type="Int32" Name="connectivity" format="ascii">', connectivity, b"        </DataArray>",
+            b'        <DataArray type="Int32" Name="offsets" format="ascii">', offsets, b"        </DataArray>",
+            b'        <DataArray type="UInt8" Name="types" format="ascii">', types,
+            b"        </DataArray>", b"      </Cells>", b"    </Piece>", b"  </UnstructuredGrid>", b"</VTKFile>", b""]
+    with open(path, "wb") as f:
+        f.write(b"\n".join(out))
+
+
 def write_vtu(path, points, values, field_names=FIELD_NAMES, point_data=(), cell_data=()):
-    """vtk.hpp:574-667.  points [n_cells][27][3], values [n_cells][27][K]; point_data = [(name, array[n_cells*27])],
-    cell_data = [(name, array[n_cells])]."""
+    """One part's piece with every number formatted on the host.  points [n_cells][27][3], values [n_cells][27][K];
+    point_data = [(name, array[n_cells*27])], cell_data = [(name, array[n_cells])]."""
     n_cells = points.shape[0]
     n_points = n_cells * 27
     flat = values.reshape(n_points, -1)
-    out = ['<VTKFile type="UnstructuredGrid" version="1.0" byte_order="LittleEndian" header_type="UInt64">',
-           "  <UnstructuredGrid>", f'    <Piece NumberOfPoints="{n_points}" NumberOfCells="{n_cells}">',
-           "      <PointData>"]
-    for k, name in enumerate(field_names):
-        out += [f'        <DataArray type="Float64" Name="{name}" format="ascii">', _ascii(flat[:, k]),
-                "        </DataArray>"]
-    for name, array in point_data:
-        out += [f'        <DataArray type="Float64" Name="{name}" format="ascii">', _ascii(np.asarray(array).reshape(-1)),
-                "        </DataArray>"]
-    out += ["      </PointData>", "      <CellData>"]
-    for name, array in cell_data:
-        out += [f'        <DataArray type="Float64" Name="{name}" format="ascii">', _ascii(np.asarray(array).reshape(-1)),
-                "        </DataArray>"]
-    out += ["      </CellData>", "      <Points>",
-            '        <DataArray type="Float64" Name="Points" NumberOfComponents="3" format="binary">',
-            _base64_block(points.astype(np.float64)), "        </DataArray>", "      </Points>", "      <Cells>",
-            '        <DataArray type="Int32" Name="connectivity" format="ascii">',
-            "".join("%d " % i for i in range(n_points)), "        </DataArray>",
-            '        <DataArray type="Int32" Name="offsets" format="ascii">',
-            "".join("%d " % (27 * (i + 1)) for i in range(n_cells)), "        </DataArray>",
-            '        <DataArray type="UInt8" Name="types" format="ascii">', ("%d " % HEXAHEDRON27) * n_cells,
-            "        </DataArray>", "      </Cells>", "    </Piece>", "  </UnstructuredGrid>", "</VTKFile>", ""]
-    with open(path, "w") as f:
-        f.write("\n".join(out))
+    _assemble(path, n_cells, [(name, _ascii(flat[:, k]).encode()) for k, name in enumerate(field_names)],
+              [(name, _ascii(np.asarray(a).reshape(-1)).encode()) for name, a in point_data],
+              [(name, _ascii(np.asarray(a).reshape(-1)).encode()) for name, a in cell_data],
+              _base64_block(points.astype(np.float64)).encode(),
+              "".join("%d " % i for i in range(n_points)).encode(),
+              "".join("%d " % (27 * (i + 1)) for i in range(n_cells)).encode(), (b"%d " % HEXAHEDRON27) * n_cells)
 
 
 class Writer:
@@ -95,21 +99,32 @@ class Writer:
         self.cell_data.append((name, func))
 
     def WriteSolutions(self, directory, soln_name):
+        """vtk.hpp:526-668.  The values are sampled AND turned into text on the device (mcfd_sample_vtk,
+        mcfd_vtk_component_text, mcfd_format_*); the host encodes the (static) points once and writes bytes."""
         ctx = self.spatial.ctx
         part = self.spatial.part
+        n_cells = ctx.n_local
+        need_values = bool(self.point_data)          # extra point data is computed by host callbacks
         if self._points is None:
-            self._points, values = ctx.sample_vtk(self.modal, points=True)
-        else:
+            self._points, _ = ctx.sample_vtk(self.modal, points=True)
+            self._points_block = _base64_block(self._points).encode()
+            self._cells = (ctx.format_integers(n_cells * 27, 0, 1), ctx.format_integers(n_cells, 27, 27),
+                           ctx.format_integers(n_cells, HEXAHEDRON27, 0))
+        values = None
+        if need_values:
             _, values = ctx.sample_vtk(self.modal, points=False)
+        else:
+            ctx.sample_vtk_on_device(self.modal)
+        fields = [(name, ctx.vtk_component_text(k)) for k, name in enumerate(self.field_names)]
         rank, size = getattr(part, "rank", 0), getattr(part, "size", 1)
-        names = self.point_data, self.cell_data
         if rank == 0:
             os.makedirs(os.path.join(directory, soln_name), exist_ok=True)
-            write_pvtu(directory, soln_name, size, self.field_names, *names)
+            write_pvtu(directory, soln_name, size, self.field_names, self.point_data, self.cell_data)
         if self.spatial.comm is not None:
             import torch.distributed as dist
             dist.barrier(group=self.spatial.comm.group)      # part.hpp:1574
         pts = self._points.reshape(-1, 3)
-        pd = [(n, f(pts, values.reshape(len(pts), -1))) for n, f in self.point_data]
-        cd = [(n, f()) for n, f in self.cell_data]
-        write_vtu(os.path.join(directory, soln_name, f"{rank}.vtu"), self._points, values, self.field_names, pd, cd)
+        pd = [(n, ctx.format_doubles(f(pts, values.reshape(len(pts), -1)))) for n, f in self.point_data]
+        cd = [(n, ctx.format_doubles(f())) for n, f in self.cell_data]
+        _assemble(os.path.join(directory, soln_name, f"{rank}.vtu"), n_cells, fields, pd, cd, self._points_block,
+                  *self._cells)

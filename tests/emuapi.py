@@ -17,7 +17,7 @@ _lib = None
 
 def build(force=False):
     deps = [SRC] + [os.path.join(HERE, "..", "minicfd_b200", "csrc", f)
-                    for f in ("kernels.cuh", "physics.cuh", "tables.hpp")]
+                    for f in ("kernels.cuh", "physics.cuh", "tables.hpp", "format.cuh")]
     if force or not os.path.exists(LIB) or any(os.path.getmtime(d) > os.path.getmtime(LIB) for d in deps):
         subprocess.check_call(["g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-ffp-contract=off",
                                "-o", LIB, SRC])
@@ -170,3 +170,22 @@ def boundary(mesh, degree, *, n_local=None, n_ghost=0, cells=None, bfaces=None, 
           _ip(cells), C.c_int64(nb), _ip(bfaces), _i32(btags), _ip(holder), _i32(hf), _i32(tg), _dp(pts))
     assert n >= 0
     return holder[:n], hf[:n], tg[:n], pts[:n]
+
+
+def format_g6(values):
+    """FormatG6 (format.cuh) on the host: (list of token bytes, unsure flags)."""
+    v = np.ascontiguousarray(values, dtype=np.float64).reshape(-1)
+    slots = np.zeros((v.size, 16), dtype=np.uint8)
+    lens = np.zeros(v.size, dtype=np.int32)
+    unsure = np.zeros(v.size, dtype=np.uint8)
+    lib().emu_format_g6(C.c_int64(v.size), _dp(v), slots.ctypes.data_as(C.c_char_p), _i32(lens),
+                        unsure.ctypes.data_as(C.c_char_p))
+    return [bytes(slots[i, :lens[i]]) for i in range(v.size)], unsure.astype(bool)
+
+
+def format_integer(values):
+    v = np.ascontiguousarray(values, dtype=np.int64).reshape(-1)
+    slots = np.zeros((v.size, 16), dtype=np.uint8)
+    lens = np.zeros(v.size, dtype=np.int32)
+    lib().emu_format_integer(C.c_int64(v.size), _ip(v), slots.ctypes.data_as(C.c_char_p), _i32(lens))
+    return [bytes(slots[i, :lens[i]]) for i in range(v.size)]

@@ -10,6 +10,7 @@
 
 #include "../../minicfd_b200/csrc/kernels.cuh"
 #include "../../minicfd_b200/csrc/tables.hpp"
+#include "../../minicfd_b200/csrc/format.cuh"
 
 using namespace mcfd;
 
@@ -391,4 +392,28 @@ void emu_riemann(int riemann, int bc_kind, const double *n, const double *ul, co
   }
 }
 
+}  // extern "C"
+
+// FormatG6 / FormatInteger (format.cuh) value by value: 16-byte token slots, lengths, and the "host must decide" flag
+extern "C" {
+void emu_format_g6(int64_t n, const double *values, char *slots, int *lens, unsigned char *unsure) {
+  static std::vector<double> table;
+  if (table.empty()) {
+    table.resize(2 * (kPow10Max - kPow10Min + 1));
+    BuildPow10Table(table.data());
+  }
+  for (int64_t i = 0; i < n; ++i) {
+    const Token t = FormatG6(values[i], table.data());
+    std::memcpy(slots + i * kTokenSlot, t.c, kTokenSlot);
+    lens[i] = t.len;
+    unsure[i] = t.unsure;
+  }
+}
+void emu_format_integer(int64_t n, const int64_t *values, char *slots, int *lens) {
+  for (int64_t i = 0; i < n; ++i) {
+    const Token t = FormatInteger(values[i]);
+    std::memcpy(slots + i * kTokenSlot, t.c, kTokenSlot);
+    lens[i] = t.len;
+  }
+}
 }  // extern "C"

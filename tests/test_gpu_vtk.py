@@ -131,3 +131,47 @@ def test_driver_writes_frames_like_the_reference(tmp_path):
         assert open(ours / (frame + ".pvtu")).read() == open(theirs / (frame + ".pvtu")).read()
         n, diff = compare_vtu(open(ours / frame / "0.vtu").read(), open(theirs / frame / "0.vtu").read())
         assert n == 300 * (27 * 5 + 5 + 27 + 2) and diff <= n // 1000
+
+
+def test_numbers_formatted_on_the_device_equal_printf():
+    """mcfd_format_doubles / mcfd_format_integers: the packed text equals `"%g " % v` for every value, including the
+    ones the device hands to the host (ties, denormals, huge values), NaNs, infinities and signed zeros."""
+    import test_vtk_format as fmt
+    g = np.load(os.path.join(GOLDEN, "vtk_nodal_p2.npz"))
+    sp = spatial_for(g, 2, "nodal")
+    rng = np.random.default_rng(11)
+    mant = rng.uniform(-10, 10, 300000)
+    values = np.concatenate([fmt._special_values(), mant, mant * 10.0 ** rng.integers(-30, 30, mant.size),
+                             np.round(rng.uniform(-1e7, 1e7, 50000)), np.round(rng.uniform(-100, 100, 50000), 2)])
+    expect = b"".join(b"%g " % v for v in values)
+    assert bytes(sp.ctx.format_doubles(values)) == expect
+    assert bytes(sp.ctx.format_doubles(values[:5])) == b"".join(b"%g " % v for v in values[:5])     # scratch is reused
+    ties = np.full(70000, 12345.25)                       # more undecidable values than the device's list holds
+    assert bytes(sp.ctx.format_doubles(ties)) == b"12345.2 " * 70000
+    assert bytes(sp.ctx.format_doubles(np.zeros(0))) == b""
+    assert bytes(sp.ctx.format_integers(5000, 0, 1)) == b"".join(b"%d " % i for i in range(5000))
+    assert bytes(sp.ctx.format_integers(3000, 27, 27)) == b"".join(b"%d " % (27 * (i + 1)) for i in range(3000))
+    assert bytes(sp.ctx.format_integers(7, 29, 0)) == b"29 " * 7
+
+
+def test_component_text_equals_host_formatting_of_the_samples():
+    g = np.load(os.path.join(GOLDEN, "vtk_extrapolation_p3.npz"))
+    sp = spatial_for(g, 3, "extrapolation")
+    _, values = sp.ctx.sample_vtk(True)
+    sp.ctx.sample_vtk_on_device(True)
+    for k in range(5):
+        assert bytes(sp.ctx.vtk_component_text(k)) == b"".join(b"%g " % v for v in values[:, :, k].reshape(-1))
+
+
+def test_frame_at_size_device_text_equals_host_text(tmp_path):
+    """BASELINE config 2's mesh (42^3 cells, 2 M points): the frame written with device-side text is the file the
+    host-side formatting writes, byte for byte."""
+    m = meshmod.box(42, 42, 42, hi=(10.0, 10.0, 10.0))
+    from minicfd_b200 import fields
+    sp = Spatial(Part(m), degree=2, riemann=capi.HLLC, device=0)
+    sp.Approximate(lambda x: fields.vortex()(x, 0.3))
+    w = vtk.Writer(sp)
+    w.WriteSolutions(str(tmp_path), "Frame0")
+    points, values = sp.ctx.sample_vtk(False)
+    vtk.write_vtu(str(tmp_path / "host.vtu"), points, values)
+    assert open(tmp_path / "Frame0" / "0.vtu", "rb").read() == open(tmp_path / "host.vtu", "rb").read()
