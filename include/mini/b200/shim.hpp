@@ -145,6 +145,14 @@ struct IdealGasTag {
   static_assert(kGammaTimes10 == 14, "gamma = 1.4 (demo/euler/sourceless.hpp:21)");
   static constexpr S Gamma() { return 1.4; }
   static constexpr S R() { return 287.05; }
+  // host-callable converters the drivers' initial and boundary conditions use (types.hpp:248-287)
+  static S GetSpeedOfSound(S temperature) { return temperature > 0 ? std::sqrt(Gamma() * R() * temperature) : 0; }
+  static S GetSpeedOfSound(S rho, S p) { return (rho > 0 && p > 0) ? std::sqrt(Gamma() * p / rho) : 0; }
+  static S GetMachFactor(S mach) { return 1 + (Gamma() - 1) / 2 * mach * mach; }
+  static S TotalTemperatureToTemperature(S mach, S total_temperature) { return total_temperature / GetMachFactor(mach); }
+  static S TotalPressureToPressure(S mach, S total_pressure) {
+    return total_pressure / std::pow(GetMachFactor(mach), Gamma() / (Gamma() - 1));
+  }
   // types.hpp:302-311
   static Conservatives<S, 3> PrimitiveToConservative(Primitives<S, 3> const &q) {
     Conservatives<S, 3> c;

@@ -908,6 +908,12 @@ static SolverBase *Create(int scheme, int riemann, GlobalMesh &&mesh) {
     case 0: return new SolverImpl<sp::WithLimiter<sp::fr::Lobatto<ModalPart, RExact>, Lazy>>(std::move(mesh));
     case 1: return new SolverImpl<sp::WithLimiter<sp::fr::Lobatto<ModalPart, RHllc>, Lazy>>(std::move(mesh));
     }
+  } else if (scheme == 13) {  // WithLimiter<dg::Lobatto, weno::Lazy> (demo/euler/sourceless.hpp:67-69, 76-80: DGSEM + LIMITER)
+    using Lazy = mini::limiter::weno::Lazy<typename ModalPart::Cell>;
+    switch (riemann) {
+    case 0: return new SolverImpl<sp::WithLimiter<sp::dg::Lobatto<ModalPart, RExact>, Lazy>>(std::move(mesh));
+    case 1: return new SolverImpl<sp::WithLimiter<sp::dg::Lobatto<ModalPart, RHllc>, Lazy>>(std::move(mesh));
+    }
   } else if (scheme == 5) {   // WithLimiter<fr::Lobatto, weno::Eigen> (demo/euler/rotorcraft.hpp:41 names the limiter so)
     using Cell = typename ModalPart::Cell;
     switch (riemann) {

@@ -260,3 +260,159 @@ def test_lid_driven_cavity_driver_through_cpp_template_api(tmp_path, k_local):
     assert got.shape == ref.shape == (n * n * 2 * 135,)
     assert np.abs(got[1::5]).max() > 1e-7      # the lid has set the fluid in motion (det-scaled when kLocal)
     assert np.abs(got - ref).max() / np.abs(ref).max() < 1e-12
+
+
+def _graded_box(xs, ys, zs, retag=None):
+    """The box of demo/box_mesh.hpp: node coordinates xs x ys x zs; retag(face_centres, tags) may rename sections."""
+    nx, ny, nz = len(xs) - 1, len(ys) - 1, len(zs) - 1
+    m = meshmod.box(nx, ny, nz, hi=(float(nx), float(ny), float(nz)))
+    idx = np.rint(m.nodes).astype(int)
+    nodes = np.stack([np.asarray(xs)[idx[:, 0]], np.asarray(ys)[idx[:, 1]], np.asarray(zs)[idx[:, 2]]], axis=1)
+    btags = m.btags.copy()
+    if retag is not None:
+        btags = retag(nodes[m.bfaces].mean(axis=1), btags)
+    return meshmod.HexMesh(nodes=nodes, cells=m.cells, bfaces=m.bfaces, btags=btags)
+
+
+def _uniform(lo, hi, n):
+    return [lo + (hi - lo) * i / n for i in range(n + 1)]        # demo::Uniform, same operation order
+
+
+def _double_mach_reference(n_steps, per_unit):
+    """demo/euler/double_mach.cpp of the reference (IC, moving-shock inlets, outlets, walls) on
+    WithLimiter<dg::Lobatto<Part<Extrapolation<Hexahedron>>>, weno::Lazy>: the DGSEM + LIMITER build."""
+    import math
+    nx, ny = 4 * per_unit, per_unit
+    gap_cells = round(per_unit / 6.0)
+    GAP = 6
+    def retag(centres, tags):
+        tags = tags.copy()
+        tags[(tags == meshmod.YMIN) & (centres[:, 0] < gap_cells / per_unit)] = GAP
+        return tags
+    m = _graded_box(_uniform(0, 4, nx), _uniform(0, 1, ny), _uniform(0, 2.0 / per_unit, 2), retag)
+    rho_b, p_b, mach = 1.4, 1.0, 10.0
+    rho_a = rho_b * (mach * mach * 2.4 / 2.0) / (1.0 + mach * mach * 0.4 / 2.0)
+    p_a = p_b * (mach * mach * 1.4 - 0.4 / 2.0) / (2.4 / 2.0)
+    u_n = mach * (rho_a - rho_b) / rho_a
+    tan_60 = math.sqrt(3.0); cos_30 = tan_60 * 0.5
+    u_a, v_a = u_n * cos_30, u_n * (-0.5)
+    after = np.array([rho_a, rho_a * u_a, rho_a * v_a, rho_a * 0.0, p_a * (1 / (1.4 - 1)) + rho_a * (0.5 * (u_a * u_a + v_a * v_a + 0.0))])
+    before = np.array([rho_b, 0.0, 0.0, 0.0, p_b * (1 / (1.4 - 1)) + rho_b * 0.0])
+    x_gap, u_x = 1.0 / 6.0, mach / cos_30
+    def shock(tag, xyz, t, out, user):
+        v = after if (xyz[0] - (x_gap + u_x * t)) * tan_60 < xyz[1] else before
+        for k in range(5):
+            out[k] = v[k]
+    r = refapi.Ref(m, degree=2, scheme=refapi.DG_WENO_LAZY, riemann=1, weno=(0.001, 1e-6))
+    r.approximate(refapi.F_CALLBACK, cb=shock)        # WithLimiter::Approximate limits once ...
+    r.set_solution(r.get_solution())                   # ... and the driver calls Reconstruct once more
+    r.set_bc(meshmod.YMAX, refapi.SUPERSONIC_INLET, refapi.F_CALLBACK, cb=shock)
+    r.set_bc(meshmod.XMIN, refapi.SUPERSONIC_INLET, refapi.F_CALLBACK, cb=shock)
+    for tag in (meshmod.ZMIN, meshmod.ZMAX, meshmod.YMIN):
+        r.set_bc(tag, refapi.WALL)
+    r.set_bc(meshmod.XMAX, refapi.SUPERSONIC_OUTLET)
+    r.set_bc(GAP, refapi.SUPERSONIC_OUTLET)
+    t, dt_max = 0.0, 0.2 / 2000
+    for _ in range(n_steps):
+        dt = r.time_step(dt_max, 3)
+        r.rk_update(3, t, dt, 1)
+        t += dt
+    return r.get_solution()
+
+
+def test_double_mach_driver_through_cpp_template_api(tmp_path):
+    """BASELINE config 3 through the template API: dg::Lobatto on Extrapolation<Hexahedron> with weno::Lazy(1e-3, 1e-6),
+    time-dependent supersonic inlets (the moving shock), supersonic outlets, walls; reduced to 20 x 5 x 2 cells."""
+    if not refapi.available(2):
+        pytest.skip("oracle/_ref not shipped")
+    exe = tmp_path / "double_mach"
+    subprocess.check_call(["g++", "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "demo", "euler", "double_mach.cpp"), "-o", str(exe),
+                           "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200",
+                           "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")])
+    out = tmp_path / "column.bin"
+    res = subprocess.run([str(exe), "8", str(out), "", "5"], capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout + res.stderr
+    got = np.fromfile(out, dtype=np.float64)
+    ref = _double_mach_reference(8, 5)
+    assert got.shape == ref.shape == (200 * 135,)
+    assert np.abs(got - ref).max() / np.abs(ref).max() < 1e-10
+
+
+def _thickness_ratio(y_0, y_n, d_0, n):
+    r = 1.01                                                       # demo::ThicknessRatio, same operation order
+    for _ in range(200):
+        f = (r ** n - 1) / (r - 1) - (y_n - y_0) / d_0
+        df = n * r ** (n - 1) / (r - 1) - (r ** n - 1) / ((r - 1) * (r - 1))
+        step = f / df
+        r -= step
+        if abs(step) < 1e-15:
+            break
+    return r
+
+
+def _layers(y_0, y_n, r, n):
+    d_0 = (y_n - y_0) * (r - 1) / (r ** n - 1)
+    y = [y_0 + (r ** i - 1) / (r - 1) * d_0 for i in range(n + 1)]
+    y[n] = y_n
+    return y
+
+
+def _blasius_reference(n_steps, coarse, dt_max):
+    """demo/laminar/blasius.cpp of the reference on fr::Lobatto<Part<Hexahedron<..., true>>, ConvectionDiffusion<...>>."""
+    import math
+    n = 64 >> coarse
+    a_x = _thickness_ratio(0, 0.2, 1e-4, 64) ** (1 << coarse)
+    a_y = _thickness_ratio(0, 0.02, 1e-5, 64) ** (1 << coarse)
+    m = _graded_box(_layers(0, 0.2, a_x, n), _layers(0, 0.02, a_y, n), _uniform(0, 0.1, 3))
+    mach, p0, t0 = 0.2, 104165.0, 290.304
+    factor = 1 + (1.4 - 1) / 2 * mach * mach
+    p_inf = p0 / math.pow(factor, 1.4 / (1.4 - 1))
+    t_inf = t0 / factor
+    rho_inf = p_inf / t_inf / 287.05
+    u_inf = mach * math.sqrt(1.4 * p_inf / rho_inf)
+    def cons(rho, u, p):
+        return [rho, rho * u, rho * 0.0, rho * 0.0, p * (1 / (1.4 - 1)) + rho * (0.5 * (u * u + 0.0 + 0.0))]
+    def ic(tag, xyz, t, out, user):
+        u_bottom = u_inf * (1 - xyz[0] / 0.2)
+        du_dy = (u_inf - u_bottom) / 0.02
+        v = cons(rho_inf, du_dy * xyz[1] + u_bottom, p_inf)
+        for k in range(5):
+            out[k] = v[k]
+    far = cons(rho_inf, u_inf, p_inf)
+    r = refapi.Ref(m, degree=2, scheme=refapi.FR_LOCAL_VISCOUS, riemann=1)
+    r.set_viscous(2.0, 1.0 / 12, 1.57e-5, 0.708)
+    r.approximate(refapi.F_CALLBACK, cb=ic)
+    r.set_bc(meshmod.XMIN, refapi.SMART, refapi.F_CONST, far)
+    r.set_bc(meshmod.XMAX, refapi.SUBSONIC_OUTLET, refapi.F_CONST, [0, 0, 0, 0, p_inf])
+    r.set_bc(meshmod.YMAX, refapi.SMART, refapi.F_CONST, far)
+    r.set_bc(meshmod.YMIN, refapi.NO_SLIP, refapi.F_CONST, [0, 0, 0, 0, 0])
+    for tag in (meshmod.ZMIN, meshmod.ZMAX):
+        r.set_bc(tag, refapi.WALL)
+    t = 0.0
+    for _ in range(n_steps):
+        dt = r.time_step(dt_max, 3)
+        r.rk_update(3, t, dt, 1)
+        t += dt
+    return r.get_solution()
+
+
+def test_blasius_driver_through_cpp_template_api(tmp_path):
+    """BASELINE config 4 through the template API: FR on Hexahedron<..., true>, HLLC + direct DG (beta = 2, 1/12),
+    nu = 1.57e-5, the graded plate mesh (cell aspect ratios in the hundreds) coarsened to 8 x 8 x 3, smart far field,
+    subsonic outlet, no-slip plate."""
+    if not refapi.available(2):
+        pytest.skip("oracle/_ref not shipped")
+    exe = tmp_path / "blasius"
+    subprocess.check_call(["g++", "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "demo", "laminar", "blasius.cpp"), "-o", str(exe),
+                           "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200",
+                           "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")])
+    out = tmp_path / "column.bin"
+    res = subprocess.run([str(exe), "10", str(out), "3", "3", "1e-7"], capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout + res.stderr
+    got = np.fromfile(out, dtype=np.float64)
+    ref = _blasius_reference(10, 3, 1e-7)
+    assert got.shape == ref.shape == (8 * 8 * 3 * 135,)
+    assert np.isfinite(ref).all()
+    assert np.abs(got - ref).max() / np.abs(ref).max() < 1e-11
