@@ -313,6 +313,25 @@ int mcfd_format_doubles(mcfd_ctx *ctx, int64_t n, const double *values, char *te
 int mcfd_format_integers(mcfd_ctx *ctx, int64_t n, int64_t first, int64_t step, char *text, int64_t capacity,
                          int64_t *length);
 
+/* The step before the path: the deterministic index work of mini::mesh::Shuffler that turns a cell partition (METIS's
+ * output, which stays with the host) into the part-contiguous numbering the solver reads.  Context-free: `device` is
+ * the CUDA ordinal, all arrays are host arrays, results are bit-exact.
+ * mcfd_get_node_parts = metis::GetNodeParts (include/mini/mesh/metis.hpp:314-335): a node belongs to the smallest part
+ *   among the cells that use it; range[n_cells + 1] / nodes[] are the mesh's CSR lists (0-based), untouched nodes get
+ *   n_parts.
+ * mcfd_get_new_order = GetNewOrder (include/mini/mesh/shuffler.hpp:35-49): indices sorted by (part, index);
+ *   new_to_old[n], old_to_new[n].
+ * mcfd_shuffle_data = ShuffleData (shuffler.hpp:57-64) on rows of `width` doubles, in place.
+ * mcfd_shuffle_connectivity = ShuffleConnectivity (shuffler.hpp:85-105): 1-based node ids renamed through
+ *   old_to_new_for_nodes[n_nodes], then the cells' rows of `npe` ids reordered by new_to_old_for_cells, in place. */
+int mcfd_get_node_parts(int32_t device, int64_t n_nodes, int64_t n_cells, const int64_t *range, const int64_t *nodes,
+                        const int64_t *cell_parts, int64_t n_parts, int64_t *node_parts);
+int mcfd_get_new_order(int32_t device, int64_t n, const int64_t *parts, int64_t *new_to_old, int64_t *old_to_new);
+int mcfd_shuffle_data(int32_t device, int64_t n, int64_t width, const int64_t *new_to_old, double *data);
+int mcfd_shuffle_connectivity(int32_t device, int64_t n_cells, int32_t npe, int64_t n_nodes,
+                              const int64_t *old_to_new_for_nodes, const int64_t *new_to_old_for_cells,
+                              int64_t *cell_nodes);
+
 /* Initial-condition clean-up on the current solution of the local cells: kind 0 =
  * mini::limiter::average::Reconstruct (include/mini/limiter/average.hpp:11-28), kind 1 =
  * mini::limiter::majority::Reconstruct (include/mini/limiter/majority.hpp:14-42), as called by

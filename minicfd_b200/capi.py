@@ -65,6 +65,10 @@ SYMBOLS = {
     "mcfd_get_quadrature_points": (C.c_int, [_P, _D]),
     "mcfd_get_jacobian_determinants": (C.c_int, [_P, _D]),
     "mcfd_sample_vtk": (C.c_int, [_P, C.c_int32, _D, _D]),
+    "mcfd_get_node_parts": (C.c_int, [C.c_int32, C.c_int64, C.c_int64, _I64, _I64, _I64, C.c_int64, _I64]),
+    "mcfd_get_new_order": (C.c_int, [C.c_int32, C.c_int64, _I64, _I64, _I64]),
+    "mcfd_shuffle_data": (C.c_int, [C.c_int32, C.c_int64, C.c_int64, _I64, _D]),
+    "mcfd_shuffle_connectivity": (C.c_int, [C.c_int32, C.c_int64, C.c_int32, C.c_int64, _I64, _I64, _I64]),
     "mcfd_vtk_component_text": (C.c_int, [_P, C.c_int32, C.c_char_p, C.c_int64, _I64]),
     "mcfd_format_doubles": (C.c_int, [_P, C.c_int64, _D, C.c_char_p, C.c_int64, _I64]),
     "mcfd_format_integers": (C.c_int, [_P, C.c_int64, C.c_int64, C.c_int64, C.c_char_p, C.c_int64, _I64]),

@@ -12,6 +12,7 @@
 #include "../../include/minicfd_b200.h"
 #include "kernels.cuh"
 #include "format.cuh"
+#include "shuffle.cuh"
 #include "tables.hpp"
 
 using namespace mcfd;
@@ -1396,6 +1397,119 @@ int mcfd_vtk_component_text(mcfd_ctx *ctx, int32_t component, char *text, int64_
   const int64_t n = ctx->mesh.n_local * 27;
   if (ctx->vtk_values.n < (size_t)n * 5) return Fail(ctx, MCFD_ERR_STATE, "call mcfd_sample_vtk first");
   return FormatAndPack(ctx, 0, ctx->vtk_values.p + component, 5, n, 0, 0, text, capacity, length);
+}
+
+// ---- the partition's index work (shuffle.cuh): context-free, host arrays in and out ---------------------------------
+#define MCFD_CUDA0(what, call)                                                                                   \
+  do {                                                                                                           \
+    cudaError_t e_ = (call);                                                                                     \
+    if (e_ != cudaSuccess) return Fail(nullptr, MCFD_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e_)); \
+  } while (0)
+
+}  // extern "C"
+template <class T>
+static cudaError_t Upload(DevBuf<T> *buf, const T *host, size_t n) {
+  cudaError_t e = buf->Alloc(n);
+  if (e != cudaSuccess || n == 0) return e;
+  return cudaMemcpy(buf->p, host, n * sizeof(T), cudaMemcpyHostToDevice);
+}
+extern "C" {
+static int Blocks(int64_t n, int threads) { return (int)((n + threads - 1) / threads); }
+
+int mcfd_get_node_parts(int32_t device, int64_t n_nodes, int64_t n_cells, const int64_t *range, const int64_t *nodes,
+    const int64_t *cell_parts, int64_t n_parts, int64_t *node_parts) {
+  const char *me = "mcfd_get_node_parts";
+  if (n_nodes < 0 || n_cells < 0 || !range || !nodes || !cell_parts || !node_parts)
+    return Fail(nullptr, MCFD_ERR_ARG, std::string(me) + ": null pointer or negative size");
+  const int64_t n_entries = range[n_cells] - range[0];
+  if (range[0] != 0 || n_entries < 0) return Fail(nullptr, MCFD_ERR_ARG, std::string(me) + ": range must start at 0 and grow");
+  for (int64_t j = 0; j < n_entries; ++j)
+    if (nodes[j] < 0 || nodes[j] >= n_nodes) return Fail(nullptr, MCFD_ERR_ARG, std::string(me) + ": node index out of range");
+  MCFD_CUDA0(me, cudaSetDevice(device));
+  DevBuf<long long> d_range, d_nodes, d_parts, d_out;
+  MCFD_CUDA0(me, Upload(&d_range, (const long long *)range, (size_t)n_cells + 1));
+  MCFD_CUDA0(me, Upload(&d_nodes, (const long long *)nodes, (size_t)n_entries));
+  MCFD_CUDA0(me, Upload(&d_parts, (const long long *)cell_parts, (size_t)n_cells));
+  MCFD_CUDA0(me, d_out.Alloc((size_t)n_nodes));
+  if (n_nodes) FillKernel<<<Blocks(n_nodes, 256), 256>>>(d_out.p, n_nodes, n_parts);   // metis.hpp:319
+  if (n_entries) NodePartsKernel<<<Blocks(n_entries, 256), 256>>>(d_range.p, d_nodes.p, d_parts.p, n_cells, n_entries, d_out.p);
+  MCFD_CUDA0(me, cudaGetLastError());
+  MCFD_CUDA0(me, cudaMemcpy(node_parts, d_out.p, (size_t)n_nodes * sizeof(int64_t), cudaMemcpyDeviceToHost));
+  return MCFD_OK;
+}
+
+int mcfd_get_new_order(int32_t device, int64_t n, const int64_t *parts, int64_t *new_to_old, int64_t *old_to_new) {
+  const char *me = "mcfd_get_new_order";
+  if (n < 0 || (n > 0 && (!parts || !new_to_old || !old_to_new)))
+    return Fail(nullptr, MCFD_ERR_ARG, std::string(me) + ": null pointer or negative size");
+  if (n == 0) return MCFD_OK;
+  int64_t n_parts = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    if (parts[i] < 0) return Fail(nullptr, MCFD_ERR_ARG, std::string(me) + ": negative part");
+    n_parts = std::max(n_parts, parts[i] + 1);
+  }
+  const int64_t n_chunks = (n + kSortChunk - 1) / kSortChunk, table = n_parts * n_chunks;
+  if (table > (int64_t)1 << 28) return Fail(nullptr, MCFD_ERR_ARG, std::string(me) + ": parts x chunks table too large");
+  MCFD_CUDA0(me, cudaSetDevice(device));
+  DevBuf<long long> d_parts, d_n2o, d_o2n;
+  DevBuf<unsigned int> d_hist, d_running;
+  DevBuf<unsigned long long> d_base;
+  MCFD_CUDA0(me, Upload(&d_parts, (const long long *)parts, (size_t)n));
+  MCFD_CUDA0(me, d_n2o.Alloc(n));
+  MCFD_CUDA0(me, d_o2n.Alloc(n));
+  MCFD_CUDA0(me, d_hist.Alloc(table));
+  MCFD_CUDA0(me, d_running.Alloc(table));
+  MCFD_CUDA0(me, d_base.Alloc(table + 1));
+  MCFD_CUDA0(me, cudaMemset(d_hist.p, 0, table * sizeof(unsigned int)));
+  MCFD_CUDA0(me, cudaMemset(d_running.p, 0, table * sizeof(unsigned int)));
+  PartHistogramKernel<<<(int)n_chunks, 256>>>(d_parts.p, n, (int)n_parts, n_chunks, d_hist.p);
+  TokenScanKernel<<<1, 1024>>>(d_hist.p, (int)table, d_base.p);     // exclusive scan, part-major = the sorted order
+  PartScatterKernel<<<(int)n_chunks, 32>>>(d_parts.p, n, n_chunks, d_base.p, d_running.p, d_n2o.p, d_o2n.p);
+  MCFD_CUDA0(me, cudaGetLastError());
+  MCFD_CUDA0(me, cudaMemcpy(new_to_old, d_n2o.p, n * sizeof(int64_t), cudaMemcpyDeviceToHost));
+  MCFD_CUDA0(me, cudaMemcpy(old_to_new, d_o2n.p, n * sizeof(int64_t), cudaMemcpyDeviceToHost));
+  return MCFD_OK;
+}
+
+int mcfd_shuffle_data(int32_t device, int64_t n, int64_t width, const int64_t *new_to_old, double *data) {
+  const char *me = "mcfd_shuffle_data";
+  if (n < 0 || width <= 0 || (n > 0 && (!new_to_old || !data)))
+    return Fail(nullptr, MCFD_ERR_ARG, std::string(me) + ": null pointer or bad size");
+  if (n == 0) return MCFD_OK;
+  for (int64_t i = 0; i < n; ++i)
+    if (new_to_old[i] < 0 || new_to_old[i] >= n) return Fail(nullptr, MCFD_ERR_ARG, std::string(me) + ": index out of range");
+  MCFD_CUDA0(me, cudaSetDevice(device));
+  DevBuf<long long> d_order;
+  DevBuf<double> d_src, d_dst;
+  MCFD_CUDA0(me, Upload(&d_order, (const long long *)new_to_old, (size_t)n));
+  MCFD_CUDA0(me, Upload(&d_src, (const double *)data, (size_t)(n * width)));
+  MCFD_CUDA0(me, d_dst.Alloc(n * width));
+  GatherRowsKernel<<<Blocks(n * width, 256), 256>>>(d_src.p, d_dst.p, d_order.p, n, width);
+  MCFD_CUDA0(me, cudaGetLastError());
+  MCFD_CUDA0(me, cudaMemcpy(data, d_dst.p, n * width * sizeof(double), cudaMemcpyDeviceToHost));
+  return MCFD_OK;
+}
+
+int mcfd_shuffle_connectivity(int32_t device, int64_t n_cells, int32_t npe, int64_t n_nodes,
+    const int64_t *old_to_new_for_nodes, const int64_t *new_to_old_for_cells, int64_t *cell_nodes) {
+  const char *me = "mcfd_shuffle_connectivity";
+  if (n_cells < 0 || npe <= 0 || n_nodes < 0 || (n_cells > 0 && (!old_to_new_for_nodes || !new_to_old_for_cells || !cell_nodes)))
+    return Fail(nullptr, MCFD_ERR_ARG, std::string(me) + ": null pointer or bad size");
+  if (n_cells == 0) return MCFD_OK;
+  for (int64_t i = 0; i < n_cells * npe; ++i)   // the reference's .at() (shuffler.hpp:94) throws on such input
+    if (cell_nodes[i] < 1 || cell_nodes[i] > n_nodes) return Fail(nullptr, MCFD_ERR_ARG, std::string(me) + ": node id out of range (ids are 1-based)");
+  for (int64_t i = 0; i < n_cells; ++i)
+    if (new_to_old_for_cells[i] < 0 || new_to_old_for_cells[i] >= n_cells) return Fail(nullptr, MCFD_ERR_ARG, std::string(me) + ": cell index out of range");
+  MCFD_CUDA0(me, cudaSetDevice(device));
+  DevBuf<long long> d_nodes, d_cells, d_old, d_new;
+  MCFD_CUDA0(me, Upload(&d_nodes, (const long long *)old_to_new_for_nodes, (size_t)n_nodes));
+  MCFD_CUDA0(me, Upload(&d_cells, (const long long *)new_to_old_for_cells, (size_t)n_cells));
+  MCFD_CUDA0(me, Upload(&d_old, (const long long *)cell_nodes, (size_t)(n_cells * npe)));
+  MCFD_CUDA0(me, d_new.Alloc(n_cells * npe));
+  ShuffleConnectivityKernel<<<Blocks(n_cells * npe, 256), 256>>>(d_old.p, d_new.p, d_nodes.p, d_cells.p, n_cells, npe);
+  MCFD_CUDA0(me, cudaGetLastError());
+  MCFD_CUDA0(me, cudaMemcpy(cell_nodes, d_new.p, n_cells * npe * sizeof(int64_t), cudaMemcpyDeviceToHost));
+  return MCFD_OK;
 }
 
 int64_t mcfd_launch_count(const mcfd_ctx *ctx) { return ctx ? ctx->launches : 0; }
