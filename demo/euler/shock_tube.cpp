@@ -28,7 +28,10 @@ using Unrotated = mini::riemann::euler::Exact<Gas, kDimensions>;
 using Riemann = mini::riemann::rotated::Euler<Unrotated>;
 
 constexpr int kComponents = 5;
-constexpr int kDegrees = 2;
+#ifndef DEGREE
+#define DEGREE 2   // demo/euler/sourceless.hpp:27; -DDEGREE=3 for the p = 3 schemes
+#endif
+constexpr int kDegrees = DEGREE;
 #ifdef DGFEM   // demo/euler/sourceless.hpp:28-33
 #include "mini/integrator/legendre.hpp"
 using Gx = mini::integrator::Legendre<Scalar, kDegrees + 1>;
@@ -89,7 +92,7 @@ using Spatial = Unlimited;
 #include "mini/mesh/vtk.hpp"
 using VtkWriter = mini::mesh::vtk::Writer<Part>;   // demo/euler/sourceless.cpp:38
 #include "mini/temporal/rk.hpp"
-constexpr int kOrders = 3;
+constexpr int kOrders = std::min(3, kDegrees + 1);   // demo/euler/sourceless.hpp:110
 using Temporal = mini::temporal::RungeKutta<kOrders, Scalar>;
 
 // demo/euler/shock_tube.cpp:5-26 of the reference

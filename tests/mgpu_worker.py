@@ -92,6 +92,29 @@ def energy(sp, comm, m, parts, part, degree, rank, world):
     finish(comm, ok, rank)
 
 
+def check_frame(directory, m, parts, world, degree, column):
+    """The N pieces, read back and put in global cell order, against the samples of a single-part context that holds
+    the gathered solution (six printed digits)."""
+    import shutil
+    pvtu = open(os.path.join(directory, "Frame1.pvtu")).read()
+    pieces_named = all(f'<Piece Source="./Frame1/{k}.vtu"/>' in pvtu for k in range(world)) and pvtu.count("<Piece ") == world
+    whole = Spatial(Part(m), degree=degree, riemann=capi.HLLC, device=torch.cuda.current_device())
+    whole.SetSolutionColumn(column)
+    _, values = whole.ctx.sample_vtk(False)
+    worst = 0.0
+    for k in range(world):
+        cells = Part(m, parts, k, world).local_global
+        lines = open(os.path.join(directory, "Frame1", f"{k}.vtu")).read().split("\n")
+        at = next(i for i, l in enumerate(lines) if 'Name="EnergyStagnationDensity"' in l)
+        got = np.array(lines[at + 1].split(), dtype=np.float64).reshape(len(cells), 27)
+        expect = values[cells][:, :, 4]
+        worst = max(worst, float(np.abs(got - expect).max() / np.abs(expect).max()))
+        pieces_named = pieces_named and f'NumberOfCells="{len(cells)}"' in lines[2]
+    shutil.rmtree(directory)
+    print(f"MGPU world={world} frame: pieces named {pieces_named}, values within {worst:.1e}")
+    return pieces_named and worst < 1.01e-5
+
+
 def main():
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
@@ -135,6 +158,18 @@ def main():
     dist.all_reduce(sol)
     dist.all_reduce(res)
     ok = True
+    frame_ok = True
+    if mode == "euler":
+        # frame output on N parts: rank 0 writes the .pvtu naming one piece per rank, every rank its own .vtu
+        # (mini::mesh::vtk::Writer<Part>::WriteSolutions, vtk.hpp:541-573, 574-667)
+        import tempfile
+        from minicfd_b200 import vtk
+        holder = [tempfile.mkdtemp() if rank == 0 else None]
+        dist.broadcast_object_list(holder, 0)
+        vtk.Writer(sp).WriteSolutions(holder[0], "Frame1")
+        dist.barrier()
+        if rank == 0:
+            frame_ok = check_frame(holder[0], m, parts, world, degree, sol.cpu().numpy())
     if rank == 0 and mode == "weno":
         # the limited result depends on the partition (limiter/reconstruct.hpp:46-51): compare with the
         # reference run on the same parts
@@ -175,7 +210,7 @@ def main():
         rref = o.residual(ref, tt)
         e_r = np.abs(res.cpu().numpy() - rref).max() / np.abs(rref).max()
         print(f"MGPU world={world} degree={degree}: solution rel err {e_u:.2e}, residual rel err {e_r:.2e}")
-        ok = e_u < 1e-12 and e_r < 1e-11
+        ok = e_u < 1e-12 and e_r < 1e-11 and frame_ok
     finish(comm, ok, rank)
 
 

@@ -17,14 +17,14 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _sod_reference(riemann, n_steps, limiter=False, eigen=False):
+def _sod_reference(riemann, n_steps, limiter=False, eigen=False, degree=2):
     """The same loop as the driver, on the CPU checker (reference binary when shipped, else the C port)."""
     m = meshmod.box(50, 2, 3, hi=(5.0, 0.2, 0.3))
     left = np.array([1.0, 0, 0, 0, 1.0 / 0.4]); right = np.array([0.125, 0, 0, 0, 0.1 / 0.4])
     dt_max = 0.2 / 200
-    if refapi.available(2):
+    if refapi.available(degree):
         scheme = (refapi.FR_WENO_EIGEN if eigen else refapi.FR_WENO_LAZY) if limiter else refapi.FR
-        r = refapi.Ref(m, degree=2, scheme=scheme, riemann=riemann)
+        r = refapi.Ref(m, degree=degree, scheme=scheme, riemann=riemann)
         def ic(tag, xyz, t, out, user):
             v = left if xyz[0] < 2.5 else right
             for k in range(5):
@@ -41,12 +41,12 @@ def _sod_reference(riemann, n_steps, limiter=False, eigen=False):
             t += dt
         return r.get_solution()
     from minicfd_b200.part import cell_points
-    o = oc.Oracle(m, 2, 0, riemann)
+    o = oc.Oracle(m, degree, 0, riemann)
     o.set_bc(meshmod.XMIN, 5, oc.F_CONST, left)
     o.set_bc(meshmod.XMAX, 5, oc.F_CONST, right)
     for tag in (meshmod.YMIN, meshmod.YMAX, meshmod.ZMIN, meshmod.ZMAX):
         o.set_bc(tag, 0)
-    x = cell_points(m.nodes, m.cells, 2)[..., 0]
+    x = cell_points(m.nodes, m.cells, degree)[..., 0]
     u = np.where((x < 2.5)[..., None], left, right).reshape(-1)
     if limiter:
         o.set_limiter(0.001, 1e-6, eigen=eigen)
@@ -131,6 +131,28 @@ def _sod_viscosity_reference(n_steps, frames=None):
     if frames:
         r.write_vtu(frames, "Frame%d" % n_steps)
     return r.get_solution(), r.cell_viscosity()
+
+
+@pytest.mark.parametrize("limiter", [False, True])
+def test_sod_driver_at_degree_three(tmp_path, limiter):
+    """-DDEGREE=3: Lobatto<Scalar, 4>, 64 nodes per cell, with and without WithLimiter<.., weno::Lazy> (20 modes).
+    Four steps only without the limiter: in the sixth step the unlimited p = 3 solution overshoots to a negative
+    pressure, which the reference zeroes (types.hpp:289-301) and then feeds to its HLLC, whose wave speeds become
+    0 * inf = NaN so that no branch of hllc.hpp:33-44 is taken and an uninitialised flux comes back -- nothing to
+    compare with (this library returns NaN there)."""
+    exe = tmp_path / "shock_tube_p3"
+    subprocess.check_call(["g++", "-DUSE_HLLC", "-DDEGREE=3", *(["-DLIMITER"] if limiter else []), "-std=c++20", "-O2",
+                           "-I", os.path.join(ROOT, "include"), os.path.join(ROOT, "demo", "euler", "shock_tube.cpp"),
+                           "-o", str(exe), "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200",
+                           "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")])
+    out = tmp_path / "column.bin"
+    n_steps = 6 if limiter else 4
+    res = subprocess.run([str(exe), str(n_steps), str(out)], capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout + res.stderr
+    got = np.fromfile(out, dtype=np.float64)
+    ref = _sod_reference(1, n_steps, limiter=limiter, degree=3)
+    assert got.shape == ref.shape == (300 * 320,)
+    assert np.abs(got - ref).max() / np.abs(ref).max() < (1e-11 if limiter else 1e-12)
 
 
 def test_sod_driver_with_energy_based_viscosity_through_cpp_template_api(tmp_path):
