@@ -542,6 +542,11 @@ struct HostMesh {
         double det = r[0][0] * (r[1][1] * r[2][2] - r[1][2] * r[2][1])
                    - r[0][1] * (r[1][0] * r[2][2] - r[1][2] * r[2][0])
                    + r[0][2] * (r[1][0] * r[2][1] - r[1][1] * r[2][0]);
+        if (!(det > 0)) {   // an inverted or degenerate cell; the reference divides by this determinant (fr/general.hpp:256-266)
+          error = "cell " + std::to_string(c) + " has a non-positive Jacobian determinant at a solution point "
+                  "(node order must be CGNS HEXA_8, right-handed)";
+          return false;
+        }
         vol += w[i] * w[j] * w[k] * det;
       }
       volume[c] = vol;
