@@ -144,9 +144,15 @@ int main(int argc, char *argv[]) {
 #endif
 #elif defined(VISCOSITY)   // demo/euler/sourceless.cpp:117-126
   Diffusion::SetProperty(0.0);
+#ifdef AS_SHIPPED   // demo/euler/shock_tube_sod.json:6, 19-21
+  Diffusion::SetBetaValues(/* ddg_beta_0 = */2.0, /* ddg_beta_1 = */0.0833333333);
+  Spatial spatial(&part);
+  RiemannWithViscosity::SetTimeScale(/* time_scale = */5.0e-2);
+#else
   Diffusion::SetBetaValues(/* ddg_beta_0 = */2.0, /* ddg_beta_1 = */1.0 / 12);
   Spatial spatial(&part);
   RiemannWithViscosity::SetTimeScale(/* time_scale = */1.0);
+#endif
   for (int k = 0; k < kComponents; ++k) {   // sourceless.cpp:122-126
     VtkWriter::AddCellData("CellViscosity" + std::to_string(k + 1),
         [k](Cell const &cell) { return RiemannWithViscosity::GetPropertyOnCell(cell.id(), 0)[k]; });
@@ -160,8 +166,12 @@ int main(int argc, char *argv[]) {
   auto cl = Gas::PrimitiveToConservative(left), cr = Gas::PrimitiveToConservative(right);
   for (int k = 0; k < 5; ++k) { given_value_left[k] = cl[k]; given_value_right[k] = cr[k]; }
   spatial.Approximate(MyIC);
-#ifdef VISCOSITY   // demo/euler/sourceless.cpp:145-153 with "initial_limiter": "average"
+#ifdef VISCOSITY   // demo/euler/sourceless.cpp:145-153; "initial_limiter": "majority" in shock_tube_sod.json
+#ifdef AS_SHIPPED
+  mini::limiter::majority::Reconstruct(spatial.part_ptr());
+#else
   mini::limiter::average::Reconstruct(spatial.part_ptr());
+#endif
   RiemannWithViscosity::Viscosity::UpdateProperties();
 #endif
   // demo/euler/shock_tube.cpp:56-66

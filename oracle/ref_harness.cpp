@@ -997,6 +997,13 @@ void REF_FN(set_viscous)(double beta_0, double beta_1, double nu, double prandtl
   oracle::IsoDiffusion::SetProperty(nu);
 }
 
+// EnergyBasedViscosity::SetTimeScale (viscosity.hpp:224-226, demo/euler/sourceless.cpp:121): class-static; call it after
+// the solver exists (Initialize resets it to 1)
+void REF_FN(set_time_scale)(double time_scale) {
+  oracle::EExact::SetTimeScale(time_scale);
+  oracle::EHllc::SetTimeScale(time_scale);
+}
+
 void *REF_FN(create)(int scheme, int riemann, Int n_nodes, const double *xyz, Int n_cells,
     const Int *cell_nodes, const int *cell_parts, int n_parts, Int n_bfaces,
     const Int *bface_nodes, const int *bface_tags) {

@@ -126,6 +126,10 @@ class Ref:
         """class statics of the reference (direct.hpp:80-83, navier_stokes.hpp:57-60): process-wide"""
         self._f("set_viscous")(C.c_double(beta0), C.c_double(beta1), C.c_double(nu), C.c_double(prandtl))
 
+    def set_time_scale(self, time_scale):
+        """EnergyBasedViscosity::SetTimeScale (scheme FR_ENERGY_VISCOSITY; after construction)"""
+        self._f("set_time_scale")(C.c_double(time_scale))
+
     def set_bc(self, tag, bc_kind, field_kind=F_CONST, params=None, cb=None):
         self._f("set_bc")(self.h, C.c_int(tag), C.c_int(bc_kind), *self._field(field_kind, params, cb))
 

@@ -102,20 +102,23 @@ def test_sod_driver_with_weno_limiter_through_cpp_template_api(tmp_path, eigen):
     assert np.abs(got - ref).max() / np.abs(ref).max() < 1e-11
 
 
-def _sod_viscosity_reference(n_steps, frames=None):
+def _sod_viscosity_reference(n_steps, frames=None, as_shipped=False):
     """Sod with WithViscosity<fr::Lobatto<Part, EnergyBasedViscosity<...>>> (the reference's VISCOSITY build)."""
     m = meshmod.box(50, 2, 3, hi=(5.0, 0.2, 0.3))
     left = np.array([1.0, 0, 0, 0, 1.0 / 0.4]); right = np.array([0.125, 0, 0, 0, 0.1 / 0.4])
     dt_max = 0.2 / 200
     if not refapi.available(2):
         return None, None
-    r = refapi.Ref(m, degree=2, scheme=refapi.FR_ENERGY_VISCOSITY, riemann=1, viscous=(2.0, 1.0 / 12, 0.0, 1.0))
+    beta_1 = 0.0833333333 if as_shipped else 1.0 / 12          # demo/euler/shock_tube_sod.json:20
+    r = refapi.Ref(m, degree=2, scheme=refapi.FR_ENERGY_VISCOSITY, riemann=1, viscous=(2.0, beta_1, 0.0, 1.0))
+    if as_shipped:
+        r.set_time_scale(5.0e-2)                                 # shock_tube_sod.json:21
     def ic(tag, xyz, t, out, user):
         v = left if xyz[0] < 2.5 else right
         for k in range(5):
             out[k] = v[k]
     r.approximate(refapi.F_CALLBACK, cb=ic)
-    r.limiter(0)                                  # average::Reconstruct(part), then ...
+    r.limiter(1 if as_shipped else 0)             # majority / average ::Reconstruct(part), then ...
     r.set_solution(r.get_solution())              # ... UpdateProperties (through WithViscosity::SetSolutionColumn)
     r.set_bc(meshmod.XMIN, refapi.SMART, refapi.F_CONST, left)
     r.set_bc(meshmod.XMAX, refapi.SMART, refapi.F_CONST, right)
@@ -155,15 +158,16 @@ def test_sod_driver_at_degree_three(tmp_path, limiter):
     assert np.abs(got - ref).max() / np.abs(ref).max() < (1e-11 if limiter else 1e-12)
 
 
-def test_sod_driver_with_energy_based_viscosity_through_cpp_template_api(tmp_path):
+@pytest.mark.parametrize("as_shipped", [False, True])
+def test_sod_driver_with_energy_based_viscosity_through_cpp_template_api(tmp_path, as_shipped):
     """-DVISCOSITY: ConvectionDiffusion<Riemann, Direct<Isotropic>> inside EnergyBasedViscosity inside fr::Lobatto inside
     WithViscosity, SetBetaValues / SetTimeScale / average::Reconstruct(part) / Viscosity::UpdateProperties() as
     demo/euler/sourceless.hpp:82-103 and sourceless.cpp:117-126, 145-153 spell them."""
-    ref, nu = _sod_viscosity_reference(10)
+    ref, nu = _sod_viscosity_reference(10, as_shipped=as_shipped)
     if ref is None:
         pytest.skip("oracle/_ref not shipped")
     exe = tmp_path / "shock_tube_viscosity"
-    subprocess.check_call(["g++", "-DUSE_HLLC", "-DVISCOSITY", "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"),
+    subprocess.check_call(["g++", "-DUSE_HLLC", "-DVISCOSITY", *(["-DAS_SHIPPED"] if as_shipped else []), "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"),
                            os.path.join(ROOT, "demo", "euler", "shock_tube.cpp"), "-o", str(exe),
                            "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200",
                            "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")])
