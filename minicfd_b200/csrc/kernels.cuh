@@ -45,6 +45,14 @@ constexpr int kMaxWarps = 16;
 #ifndef MCFD_TRACE_MINB
 #define MCFD_TRACE_MINB 2
 #endif
+// resident CTAs per SM the limiter kernels (160 threads, 43-101 KB of shared memory) are compiled for
+#ifndef MCFD_WENO_MINB
+#define MCFD_WENO_MINB 4   // p = 2: 102 registers, 20 warps per SM (1 CTA per SM ran the limiter 1.7x slower)
+#endif
+// resident one-warp CTAs per SM the modal DG stage kernel is compiled for
+#ifndef MCFD_DGM_MINB
+#define MCFD_DGM_MINB 1
+#endif
 constexpr int kP2Cells = MCFD_P2_CELLS, kP2Warps = MCFD_P2_WARPS, kP3Cells = 16, kP3Warps = 16;
 constexpr int kP2ViscousWarps = MCFD_P2_VWARPS;
 
@@ -1359,7 +1367,7 @@ __device__ __forceinline__ void WenoStage(const double *geom, const double *bas,
   __syncthreads();
 }
 template <int Q>
-__global__ void __launch_bounds__(160) ModalKernel(const double *u, const double *geom, const double *bas,
+__global__ void __launch_bounds__(160, (Q == 3 ? MCFD_WENO_MINB : 1)) ModalKernel(const double *u, const double *geom, const double *bas,
     double *mod, double *tay, int tile_begin, int cell_begin, int cell_end) {
   constexpr int P = Q - 1, N = Q * Q * Q, F = 5 * N, M = ModalShape<P>::M;
   extern __shared__ double smem[];
@@ -1372,7 +1380,7 @@ __global__ void __launch_bounds__(160) ModalKernel(const double *u, const double
       mod + ((size_t)tile * 5 * M + comp * M) * kTile + lane, tay + ((size_t)tile * 5 * M + comp * M) * kTile + lane, kTile);
 }
 template <int Q>
-__global__ void __launch_bounds__(160) WenoLazyKernel(WenoArgs p, int tile_begin) {
+__global__ void __launch_bounds__(160, (Q == 3 ? MCFD_WENO_MINB : 1)) WenoLazyKernel(WenoArgs p, int tile_begin) {
   constexpr int N = Q * Q * Q;
   extern __shared__ double smem[];
   double *sQuad = smem, *sBas = smem + N * 4 * kTile;
@@ -1437,37 +1445,64 @@ __global__ void CopyCellRowsKernel(const double *src, double *dst, int rows, int
 #endif
 
 // ---- EnergyBasedViscosity::UpdateProperties (spatial/viscosity.hpp:556-572) --------------------------------
-// One (cell, component): the jump integral over the cell's interior faces (IntegrateJumpOnFaces, :446-475; the
-// face weight is w_a w_b |J* column| from the cell's own metric, the height volume / area), the reference square
-// and speed (rotated/euler.hpp:340-355), the damping rate -u^T D u and the clamped viscosity (:477-544).
-// Returns this thread's contribution to min_dt_.  D: [tile][r*N + c][lane], nu out: [tile][comp][lane].
+// What the five components of a cell share, computed once per cell (rows `ss` doubles apart):
+//   [0, N)            quadrature weight of node n (local weight x det J): their sum is the volume
+//   [N, 2N)           lambda_max at node n (rotated/euler.hpp:340-355)
+//   [2N, 2N + 6 FQ)   weight of face point (f, q): w_a w_b |J* column| from the cell's own metric
+// `part` of `n_parts` callers split the items among themselves (the kernel's five warps; one caller on the host).
 template <int Q>
-MCFD_HD double ViscosityCell(const double *u, const double *geom, const int *nbr, const unsigned char *code,
-    const unsigned char *nbr_node, const double *damping, const double *length, int tile, int tl, int comp,
-    double time_scale, double *nu_out) {
-  constexpr int P = Q - 1, N = Q * Q * Q, F = 5 * N, FQ = Q * Q;
+struct ViscosityShape {
+  static constexpr int N = Q * Q * Q, FQ = Q * Q, kRows = 2 * N + 6 * FQ;
+  static constexpr size_t kSharedBytes = (size_t)kRows * kTile * sizeof(double) + 6 * 8 * FQ;
+};
+template <int Q>
+MCFD_HD void ViscosityShared(const double *u, const double *geom, int tile, int tl, int part, int n_parts,
+    double *sh, int ss) {
+  constexpr int N = Q * Q * Q, F = 5 * N, FQ = Q * Q;
   const double *mine = u + (size_t)tile * F * kTile + tl;
   const double *geo = geom + (size_t)tile * kGeomRows * kTile + tl;
-  double volume = 0;
-  for (int n = 0; n < N; ++n) {
+  for (int n = part; n < N; n += n_parts) {
     double d[3], w;
     QuadraturePoint<Q>(n, geo, kTile, d, &w);
-    volume += w;
+    sh[(size_t)n * ss] = w;
+    const double *s = mine + (size_t)n * 5 * kTile;
+    const Prim pr = ConsToPrim(s[0], s[kTile], s[2 * kTile], s[3 * kTile], s[4 * kTile]);
+    const double cs = SoundSpeed(pr.rho, pr.p), vel = Sqrt(pr.u * pr.u + pr.v * pr.v + pr.w * pr.w + 1e-300);
+    sh[(size_t)(N + n) * ss] = fmax(cs + vel, cs - vel);
   }
+  for (int pt = part; pt < 6 * FQ; pt += n_parts) {
+    const int f = pt / FQ, q = pt % FQ;
+    const int dir = (f == 2 || f == 4) ? 0 : ((f == 1 || f == 3) ? 1 : 2);
+    const int n = c_tab.face_node[f][q];
+    const int i = n / FQ, j = (n / Q) % Q, k = n % Q;
+    double nrm[3];
+    ComputeNormal(geo, kTile, c_tab.xi[i], c_tab.xi[j], c_tab.xi[k], dir, nrm);
+    const int ia = dir == 0 ? j : i, ib = dir == 2 ? j : k;     // the two in-face indices
+    sh[(size_t)(2 * N + pt) * ss] = c_tab.w[ia] * c_tab.w[ib] * Sqrt(nrm[0] * nrm[0] + nrm[1] * nrm[1] + nrm[2] * nrm[2]);
+  }
+}
+
+// One (cell, component): the jump integral over the cell's interior faces (IntegrateJumpOnFaces, :446-475; the
+// height is volume / area), the reference square (rotated/euler.hpp:340-355), the damping rate -u^T D u and the
+// clamped viscosity (:477-544).  Returns this thread's contribution to min_dt_.
+// D: [tile][r*N + c][lane], nu out: [tile][comp][lane]; sh: ViscosityShared's rows of this cell.
+template <int Q>
+MCFD_HD double ViscosityCell(const double *u, const int *nbr, const unsigned char *code,
+    const unsigned char *nbr_node, const double *damping, const double *length, int tile, int tl, int comp,
+    double time_scale, const double *sh, int ss, double *nu_out) {
+  constexpr int P = Q - 1, N = Q * Q * Q, F = 5 * N, FQ = Q * Q;
+  const double *mine = u + (size_t)tile * F * kTile + tl;
+  double volume = 0;
+  for (int n = 0; n < N; ++n) volume += sh[(size_t)n * ss];
   double jump = 0;
   for (int f = 0; f < 6; ++f) {
     const int nb = nbr[((size_t)tile * 6 + f) * kTile + tl];
     if (nb < 0) continue;
     const int cd = code[((size_t)tile * 6 + f) * kTile + tl];
-    const int dir = (f == 2 || f == 4) ? 0 : ((f == 1 || f == 3) ? 1 : 2);
     double area = 0, sum = 0;
     for (int q = 0; q < FQ; ++q) {
       const int n = c_tab.face_node[f][q];
-      const int i = n / FQ, j = (n / Q) % Q, k = n % Q;
-      double nrm[3];
-      ComputeNormal(geo, kTile, c_tab.xi[i], c_tab.xi[j], c_tab.xi[k], dir, nrm);
-      const int ia = dir == 0 ? j : i, ib = dir == 2 ? j : k;     // the two in-face indices
-      const double w = c_tab.w[ia] * c_tab.w[ib] * Sqrt(nrm[0] * nrm[0] + nrm[1] * nrm[1] + nrm[2] * nrm[2]);
+      const double w = sh[(size_t)(2 * N + f * FQ + q) * ss];
       const int n2 = nbr_node[((cd & 7) * 8 + ((cd >> 3) & 7)) * FQ + q];
       const double v = u[((size_t)(nb >> 5) * F + n2 * 5 + comp) * kTile + (nb & 31)];
       const double dj = mine[(size_t)(n * 5 + comp) * kTile] - v;
@@ -1478,13 +1513,12 @@ MCFD_HD double ViscosityCell(const double *u, const double *geom, const int *nbr
   }
   double max_speed = 1e-5, ref = 1e-5;
   for (int n = 0; n < N; ++n) {
-    const double *s = mine + (size_t)n * 5 * kTile;
-    const double r0 = s[0], r4 = s[4 * kTile];
-    const Prim pr = ConsToPrim(r0, s[kTile], s[2 * kTile], s[3 * kTile], r4);
-    const double cs = SoundSpeed(pr.rho, pr.p), vel = Sqrt(pr.u * pr.u + pr.v * pr.v + pr.w * pr.w + 1e-300);
-    const double lam = fmax(cs + vel, cs - vel);
+    const double lam = sh[(size_t)(N + n) * ss];
     max_speed = fmax(max_speed, lam);
-    const double sq = comp == 0 ? r0 * r0 : (comp == 4 ? r4 * r4 : r0 * r0 * lam * lam);
+    const double r0 = mine[(size_t)n * 5 * kTile];
+    double sq = r0 * r0;
+    if (comp == 4) { const double r4 = mine[(size_t)(n * 5 + 4) * kTile]; sq = r4 * r4; }
+    else if (comp != 0) sq = r0 * r0 * lam * lam;
     ref = fmax(ref, sq);
   }
   const double len = length[(size_t)tile * kTile + tl];
@@ -1511,17 +1545,24 @@ MCFD_HD double ViscosityCell(const double *u, const double *geom, const int *nbr
 }
 
 #ifdef __CUDACC__
+// thread = (cell, component): lanes = cells of the tile, warp = component; the warps first split the per-cell
+// quantities all components share (metric, wave speeds, face weights) and hand them over in shared memory
 template <int Q>
 __global__ void __launch_bounds__(160) ViscosityKernel(const double *u, const double *geom, const int *nbr,
     const unsigned char *code, const double *damping, const double *length, int n_local, double time_scale,
     double *nu_out, unsigned long long *min_dt_bits) {
-  __shared__ unsigned char sNbrNode[6 * 8 * Q * Q];
+  extern __shared__ double smem[];
+  constexpr int kRows = ViscosityShape<Q>::kRows;
+  double *sh = smem;
+  unsigned char *sNbrNode = reinterpret_cast<unsigned char *>(smem + (size_t)kRows * kTile);
   for (int i = threadIdx.x; i < 6 * 8 * Q * Q; i += 160) sNbrNode[i] = c_tab.nbr_node[i / (8 * Q * Q)][(i / (Q * Q)) % 8][i % (Q * Q)];
-  __syncthreads();
   const int tile = blockIdx.x, lane = threadIdx.x & 31, comp = threadIdx.x >> 5;
+  const bool live = tile * kTile + lane < n_local;
+  if (live) ViscosityShared<Q>(u, geom, tile, lane, comp, 5, sh + lane, kTile);
+  __syncthreads();
   double dt = 1e100;
-  if (tile * kTile + lane < n_local)
-    dt = ViscosityCell<Q>(u, geom, nbr, code, sNbrNode, damping, length, tile, lane, comp, time_scale, nu_out);
+  if (live)
+    dt = ViscosityCell<Q>(u, nbr, code, sNbrNode, damping, length, tile, lane, comp, time_scale, sh + lane, kTile, nu_out);
   for (int o = 16; o > 0; o >>= 1) dt = fmin(dt, __shfl_xor_sync(0xffffffffu, dt, o));
   if (lane == 0) atomicMin(min_dt_bits, (unsigned long long)__double_as_longlong(dt));
 }
@@ -1789,7 +1830,7 @@ MCFD_HD void DgmProjectCell(const double *values, const double *geom, const doub
 
 #ifdef __CUDACC__
 template <int Q, int kRiemann>
-__global__ void __launch_bounds__(kTile) DgmStageKernel(DgmArgs p, int tile_begin) {
+__global__ void __launch_bounds__(kTile, MCFD_DGM_MINB) DgmStageKernel(DgmArgs p, int tile_begin) {
   const int tile = tile_begin + blockIdx.x, cell = tile * kTile + threadIdx.x;
   if (cell < p.cell_begin || cell >= p.cell_end) return;
   DgmStageCell<Q, kRiemann>(p, tile, threadIdx.x);

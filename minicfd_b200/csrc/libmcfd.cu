@@ -734,10 +734,18 @@ int mcfd_update_cell_viscosity(mcfd_ctx *ctx, double time_scale) {
   double *u = HaloState(ctx);
   TimeStepResetKernel<<<1, 1, 0, ctx->stream>>>(ctx->visc_dt_bits.p);
   const int nl = (int)ctx->mesh.n_local, tiles = (nl + kTile - 1) / kTile;
-  if (ctx->q == 3) ViscosityKernel<3><<<tiles, 160, 0, ctx->stream>>>(u, ctx->geom.p, ctx->nbr.p, ctx->code.p, ctx->damping.p,
-      ctx->length.p, nl, time_scale, ctx->cell_nu.p, ctx->visc_dt_bits.p);
-  else ViscosityKernel<4><<<tiles, 160, 0, ctx->stream>>>(u, ctx->geom.p, ctx->nbr.p, ctx->code.p, ctx->damping.p,
-      ctx->length.p, nl, time_scale, ctx->cell_nu.p, ctx->visc_dt_bits.p);
+  static bool configured = false;
+  if (!configured) {
+    MCFD_CUDA(ctx, cudaFuncSetAttribute(ViscosityKernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ViscosityShape<3>::kSharedBytes));
+    MCFD_CUDA(ctx, cudaFuncSetAttribute(ViscosityKernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ViscosityShape<4>::kSharedBytes));
+    MCFD_CUDA(ctx, cudaFuncSetAttribute(ViscosityKernel<3>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    MCFD_CUDA(ctx, cudaFuncSetAttribute(ViscosityKernel<4>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    configured = true;
+  }
+  if (ctx->q == 3) ViscosityKernel<3><<<tiles, 160, ViscosityShape<3>::kSharedBytes, ctx->stream>>>(u, ctx->geom.p, ctx->nbr.p,
+      ctx->code.p, ctx->damping.p, ctx->length.p, nl, time_scale, ctx->cell_nu.p, ctx->visc_dt_bits.p);
+  else ViscosityKernel<4><<<tiles, 160, ViscosityShape<4>::kSharedBytes, ctx->stream>>>(u, ctx->geom.p, ctx->nbr.p,
+      ctx->code.p, ctx->damping.p, ctx->length.p, nl, time_scale, ctx->cell_nu.p, ctx->visc_dt_bits.p);
   MCFD_CUDA(ctx, cudaGetLastError());
   ctx->launches += 2;
   return MCFD_OK;
@@ -1086,6 +1094,9 @@ int WenoLazyBatch(mcfd_ctx *ctx, double *u, double w0, double eps, int64_t modal
     MCFD_CUDA(ctx, cudaFuncSetAttribute(ModalKernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     MCFD_CUDA(ctx, cudaFuncSetAttribute(WenoLazyKernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     MCFD_CUDA(ctx, cudaFuncSetAttribute(WenoEigenKernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // several CTAs per SM only fit when the L1/shared split is asked for the shared side
+    MCFD_CUDA(ctx, cudaFuncSetAttribute(ModalKernel<Q>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    MCFD_CUDA(ctx, cudaFuncSetAttribute(WenoLazyKernel<Q>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     configured = true;
   }
   MCFD_CUDA(ctx, EnsureTables(ctx));

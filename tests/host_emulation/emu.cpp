@@ -266,9 +266,13 @@ static void RunEnergy(HostMesh const &mesh, const double *betas, const double *c
   std::vector<unsigned char> nn(6 * 8 * Q * Q);
   for (int i = 0; i < 6 * 8 * Q * Q; ++i) nn[i] = c_tab.nbr_node[i / (8 * Q * Q)][(i / (Q * Q)) % 8][i % (Q * Q)];
   double min_dt = 1e100;
-  for (int64_t c = 0; c < nl; ++c) for (int k = 0; k < 5; ++k)
-    min_dt = std::fmin(min_dt, ViscosityCell<Q>(u.data(), geom.data(), nbr.data(), code.data(), nn.data(), damping.data(),
-        length.data(), (int)(c >> 5), (int)(c & 31), k, time_scale, nu.data()));
+  std::vector<double> shared(ViscosityShape<Q>::kRows);
+  for (int64_t c = 0; c < nl; ++c) {
+    ViscosityShared<Q>(u.data(), geom.data(), (int)(c >> 5), (int)(c & 31), 0, 1, shared.data(), 1);
+    for (int k = 0; k < 5; ++k)
+      min_dt = std::fmin(min_dt, ViscosityCell<Q>(u.data(), nbr.data(), code.data(), nn.data(), damping.data(),
+          length.data(), (int)(c >> 5), (int)(c & 31), k, time_scale, shared.data(), 1, nu.data()));
+  }
   for (int64_t c = 0; c < nl; ++c) for (int k = 0; k < 5; ++k) nu_out[c * 5 + k] = nu[((c >> 5) * 5 + k) * kTile + (c & 31)];
   *min_dt_out = min_dt;
 }
