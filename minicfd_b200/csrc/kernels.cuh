@@ -26,14 +26,17 @@ constexpr int kMaxFaceQ = kMaxQ * kMaxQ;
 constexpr int kMaxSlots = 8;    // node slots per warp
 constexpr int kMaxWarps = 16;
 // launch shape per degree: cells per CTA and warps per CTA (see StageKernel)
+// p = 2, inviscid: 16-cell CTAs of 7 warps, four per SM (55 KB of shared memory each, 72 registers): 14 node / face-point
+// items per pass leave 1 of 28 node slots and 2 of 56 point slots idle; 6 % faster than 32-cell CTAs of 10 warps, two
+// per SM (tools/run_stage_variants.sh).  The viscous kernels keep 32-cell CTAs.
 #ifndef MCFD_P2_WARPS
-#define MCFD_P2_WARPS 10
+#define MCFD_P2_WARPS 7
 #endif
 #ifndef MCFD_P2_CELLS
-#define MCFD_P2_CELLS 32
+#define MCFD_P2_CELLS 16
 #endif
 #ifndef MCFD_P2_MINB
-#define MCFD_P2_MINB 2
+#define MCFD_P2_MINB 4
 #endif
 // the viscous instantiation carries more live state per face point: its own launch shape
 #ifndef MCFD_P2_VWARPS
@@ -53,7 +56,19 @@ constexpr int kMaxWarps = 16;
 #ifndef MCFD_DGM_MINB
 #define MCFD_DGM_MINB 1
 #endif
-constexpr int kP2Cells = MCFD_P2_CELLS, kP2Warps = MCFD_P2_WARPS, kP3Cells = 16, kP3Warps = 16;
+// p = 3, inviscid: 8-cell CTAs of 8 warps, three per SM (61 KB of shared memory each, 85 registers); measured 16 %
+// faster than one 16-cell CTA of 16 warps per SM (tools/run_p3_variants.sh).  The viscous kernels keep the latter.
+#ifndef MCFD_P3_CELLS
+#define MCFD_P3_CELLS 8
+#endif
+#ifndef MCFD_P3_WARPS
+#define MCFD_P3_WARPS 8
+#endif
+#ifndef MCFD_P3_MINB
+#define MCFD_P3_MINB 3
+#endif
+constexpr int kP2Cells = MCFD_P2_CELLS, kP2Warps = MCFD_P2_WARPS, kP3Cells = MCFD_P3_CELLS, kP3Warps = MCFD_P3_WARPS;
+constexpr int kP3ViscousCells = 16, kP3ViscousWarps = 16, kP2ViscousCells = 32;
 constexpr int kP2ViscousWarps = MCFD_P2_VWARPS;
 
 // Per-degree tables, filled by the host (tables.cpp) and copied to constant memory.
@@ -885,7 +900,7 @@ MCFD_HD void StagePhaseC(const StageArgs &p, int tid, int bid, double *smem,
 // host, where RunStageBlockOnHost() below replays the phases thread by thread.
 #ifdef __CUDACC__
 template <int Q, int kRiemann, int CPB, int NW, bool kGeneral, int kViscous = kDiffNone>
-__global__ void __launch_bounds__(NW * 32, (Q == 3 ? (kViscous ? MCFD_P2_VMINB : MCFD_P2_MINB) : 1))
+__global__ void __launch_bounds__(NW * 32, (Q == 3 ? (kViscous ? MCFD_P2_VMINB : MCFD_P2_MINB) : (kViscous ? 1 : MCFD_P3_MINB)))
 StageKernel(StageArgs p) {
   extern __shared__ double smem[];
   const int tid = threadIdx.x, bid = blockIdx.x;

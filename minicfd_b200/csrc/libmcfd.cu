@@ -287,8 +287,8 @@ int LaunchStage(mcfd_ctx *ctx, const double *u_in, const double *u0, double *u_o
     e = ctx->q == 3 ? LaunchDgmQ<3>(ctx, d, (int)block_begin, (int)(block_end - block_begin))
                                 : LaunchDgmQ<4>(ctx, d, (int)block_begin, (int)(block_end - block_begin));
   } else if (ctx->cfg.diffusion != MCFD_INVISCID) {
-    e = (ctx->q == 3) ? LaunchStageViscous<3, kP2Cells, kP2ViscousWarps>(ctx, a, n_blocks)
-                      : LaunchStageViscous<4, kP3Cells, kP3Warps>(ctx, a, n_blocks);
+    e = (ctx->q == 3) ? LaunchStageViscous<3, kP2ViscousCells, kP2ViscousWarps>(ctx, a, n_blocks)
+                      : LaunchStageViscous<4, kP3ViscousCells, kP3ViscousWarps>(ctx, a, n_blocks);
   } else {
     e = (ctx->q == 3) ? LaunchStageQ<3, kP2Cells, kP2Warps>(ctx, a, n_blocks)
                       : LaunchStageQ<4, kP3Cells, kP3Warps>(ctx, a, n_blocks);
@@ -431,8 +431,9 @@ int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
   ctx->n_nodes = ctx->q * ctx->q * ctx->q;
   ctx->fields = 5 * ctx->n_nodes;
   if (config->scheme == MCFD_DG_GENERAL) ctx->fields = 5 * (ctx->q == 3 ? 10 : 20);   // K x M modal coefficients
-  ctx->cpb = (config->scheme == MCFD_DG_GENERAL) ? kTile : ((ctx->q == 3) ? kP2Cells : kP3Cells);
-  ctx->n_warps = (ctx->q == 3) ? (config->diffusion != MCFD_INVISCID ? kP2ViscousWarps : kP2Warps) : kP3Warps;
+  const bool viscous = config->diffusion != MCFD_INVISCID;
+  ctx->cpb = (config->scheme == MCFD_DG_GENERAL) ? kTile : ((ctx->q == 3) ? (viscous ? kP2ViscousCells : kP2Cells) : (viscous ? kP3ViscousCells : kP3Cells));
+  ctx->n_warps = (ctx->q == 3) ? (viscous ? kP2ViscousWarps : kP2Warps) : (viscous ? kP3ViscousWarps : kP3Warps);
   ctx->tables = BuildTables(config->degree, config->scheme, ctx->n_warps, kTile / ctx->cpb, config->fr_c_next);
   e = ctx->dt_bits.Alloc(1);
   if (e != cudaSuccess) return Fail(nullptr, MCFD_ERR_CUDA, cudaGetErrorString(e));
