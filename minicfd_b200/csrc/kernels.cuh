@@ -68,7 +68,10 @@ constexpr int kMaxWarps = 16;
 #define MCFD_P3_MINB 3
 #endif
 constexpr int kP2Cells = MCFD_P2_CELLS, kP2Warps = MCFD_P2_WARPS, kP3Cells = MCFD_P3_CELLS, kP3Warps = MCFD_P3_WARPS;
-constexpr int kP3ViscousCells = 16, kP3ViscousWarps = 16, kP2ViscousCells = 32;
+#ifndef MCFD_P2_VCELLS
+#define MCFD_P2_VCELLS 32
+#endif
+constexpr int kP3ViscousCells = 16, kP3ViscousWarps = 16, kP2ViscousCells = MCFD_P2_VCELLS;
 constexpr int kP2ViscousWarps = MCFD_P2_VWARPS;
 
 // Per-degree tables, filled by the host (tables.cpp) and copied to constant memory.

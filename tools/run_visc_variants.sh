@@ -1,7 +1,7 @@
 # A/B of launch shapes of the viscous kernels: build_variants/lib_*.so are copied over the library in turn.
 B="python bench.py --steps 20 --warmup 3 --no-cpu-baseline --no-e2e --no-graph --viscous 0.01"
 cp minicfd_b200/libminicfd_b200.so /tmp/orig.so
-for f in build_variants/lib_*.so; do
+for f in build_variants/lib_v_*.so; do
   v=$(basename $f .so)
   cp $f minicfd_b200/libminicfd_b200.so
   $B > gpurun_out/visc_$v.json 2> gpurun_out/visc_$v.err
