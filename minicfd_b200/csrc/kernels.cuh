@@ -53,6 +53,12 @@ constexpr int kMaxWarps = 16;
 #define MCFD_WENO_MINB 4   // p = 2: 102 registers, 20 warps per SM (1 CTA per SM ran the limiter 1.7x slower)
 #endif
 // resident one-warp CTAs per SM the modal DG stage kernel is compiled for
+#ifndef MCFD_WENO_P3_MINB
+#define MCFD_WENO_P3_MINB 3
+#endif
+#ifndef MCFD_WENO_P3_BAS_SHARED
+#define MCFD_WENO_P3_BAS_SHARED 0
+#endif
 #ifndef MCFD_DGM_MINB
 #define MCFD_DGM_MINB 1
 #endif
@@ -1369,6 +1375,10 @@ template <int Q>
 struct WenoShape {
   static constexpr int P = Q - 1, N = Q * Q * Q;
   static constexpr size_t kSharedBytes = (size_t)(N * 4 + ModalShape<P>::kBasRows) * kTile * sizeof(double);
+  // ModalKernel / WenoLazyKernel at p = 3 leave the basis table in global memory (L1/L2 serve it): 65 KB instead of
+  // 121 KB per CTA, so that three CTAs share an SM instead of one
+  static constexpr bool kBasInShared = MCFD_WENO_P3_BAS_SHARED || Q == 3;
+  static constexpr size_t kLazySharedBytes = kBasInShared ? kSharedBytes : (size_t)(N * 4) * kTile * sizeof(double);
 };
 template <int Q>
 __device__ __forceinline__ void WenoStage(const double *geom, const double *bas, int tile, double *sQuad, double *sBas,
@@ -1381,32 +1391,34 @@ __device__ __forceinline__ void WenoStage(const double *geom, const double *bas,
     sQuad[(n * 4 + 0) * kTile + lane] = d[0]; sQuad[(n * 4 + 1) * kTile + lane] = d[1];
     sQuad[(n * 4 + 2) * kTile + lane] = d[2]; sQuad[(n * 4 + 3) * kTile + lane] = w;
   }
-  for (int i = threadIdx.x; i < kBasRows * kTile; i += 160) sBas[i] = bas[(size_t)tile * kBasRows * kTile + i];
+  if (sBas) for (int i = threadIdx.x; i < kBasRows * kTile; i += 160) sBas[i] = bas[(size_t)tile * kBasRows * kTile + i];
   __syncthreads();
 }
 template <int Q>
-__global__ void __launch_bounds__(160, (Q == 3 ? MCFD_WENO_MINB : 1)) ModalKernel(const double *u, const double *geom, const double *bas,
+__global__ void __launch_bounds__(160, (Q == 3 ? MCFD_WENO_MINB : MCFD_WENO_P3_MINB)) ModalKernel(const double *u, const double *geom, const double *bas,
     double *mod, double *tay, int tile_begin, int cell_begin, int cell_end) {
   constexpr int P = Q - 1, N = Q * Q * Q, F = 5 * N, M = ModalShape<P>::M;
   extern __shared__ double smem[];
-  double *sQuad = smem, *sBas = smem + N * 4 * kTile;
   const int tile = tile_begin + blockIdx.x, lane = threadIdx.x & 31, comp = threadIdx.x >> 5;
+  double *sQuad = smem, *sBas = WenoShape<Q>::kBasInShared ? smem + N * 4 * kTile : nullptr;
   WenoStage<Q>(geom, bas, tile, sQuad, sBas);
+  const double *tBas = sBas ? sBas : bas + (size_t)tile * ModalShape<P>::kBasRows * kTile;
   const int cell = tile * kTile + lane;
   if (cell < cell_begin || cell >= cell_end) return;
-  ModalProjectCell<Q>(u + (size_t)tile * F * kTile + comp * kTile + lane, kTile, sQuad + lane, kTile, sBas + lane, kTile,
+  ModalProjectCell<Q>(u + (size_t)tile * F * kTile + comp * kTile + lane, kTile, sQuad + lane, kTile, tBas + lane, kTile,
       mod + ((size_t)tile * 5 * M + comp * M) * kTile + lane, tay + ((size_t)tile * 5 * M + comp * M) * kTile + lane, kTile);
 }
 template <int Q>
-__global__ void __launch_bounds__(160, (Q == 3 ? MCFD_WENO_MINB : 1)) WenoLazyKernel(WenoArgs p, int tile_begin) {
+__global__ void __launch_bounds__(160, (Q == 3 ? MCFD_WENO_MINB : MCFD_WENO_P3_MINB)) WenoLazyKernel(WenoArgs p, int tile_begin) {
   constexpr int N = Q * Q * Q;
   extern __shared__ double smem[];
-  double *sQuad = smem, *sBas = smem + N * 4 * kTile;
   const int tile = tile_begin + blockIdx.x, lane = threadIdx.x & 31, comp = threadIdx.x >> 5;
+  double *sQuad = smem, *sBas = WenoShape<Q>::kBasInShared ? smem + N * 4 * kTile : nullptr;
   WenoStage<Q>(p.geom, p.bas, tile, sQuad, sBas, p.legendre != 0);
+  const double *tBas = sBas ? sBas : p.bas + (size_t)tile * ModalShape<Q - 1>::kBasRows * kTile;
   const int cell = tile * kTile + lane;
   if (cell < p.cell_begin || cell >= p.cell_end) return;
-  WenoLazyCell<Q>(p, tile, lane, comp, sQuad + lane, kTile, sBas + lane, kTile);
+  WenoLazyCell<Q>(p, tile, lane, comp, sQuad + lane, kTile, tBas + lane, kTile);
 }
 // weno::Eigen: persistent CTAs (each owns one scratch slot) walking over the tiles of the batch
 template <int Q>

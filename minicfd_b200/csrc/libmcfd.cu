@@ -1103,7 +1103,7 @@ int WenoLazyBatch(mcfd_ctx *ctx, double *u, double w0, double eps, int64_t modal
   MCFD_CUDA(ctx, EnsureTables(ctx));
   if (modal_end > modal_begin) {   // Extrapolation::UpdateModalCoeff of the cells whose nodal values are new
     const int t0 = (int)(modal_begin / kTile), t1 = (int)((modal_end + kTile - 1) / kTile);
-    ModalKernel<Q><<<t1 - t0, 160, smem, ctx->stream>>>(u, ctx->geom.p, ctx->bas.p, ctx->mod.p, ctx->tay.p, t0,
+    ModalKernel<Q><<<t1 - t0, 160, WenoShape<Q>::kLazySharedBytes, ctx->stream>>>(u, ctx->geom.p, ctx->bas.p, ctx->mod.p, ctx->tay.p, t0,
         (int)modal_begin, (int)modal_end);
     ctx->launches++;
   }
@@ -1120,7 +1120,7 @@ int WenoLazyBatch(mcfd_ctx *ctx, double *u, double w0, double eps, int64_t modal
       const int grid = std::min(t1 - t0, kWenoEigenCtas);
       WenoEigenKernel<Q><<<grid, 160, smem, ctx->stream>>>(e, ctx->weno_scratch.p, t0, t1);
     } else {
-      WenoLazyKernel<Q><<<t1 - t0, 160, smem, ctx->stream>>>(a, t0);
+      WenoLazyKernel<Q><<<t1 - t0, 160, WenoShape<Q>::kLazySharedBytes, ctx->stream>>>(a, t0);
     }
     ctx->launches++;
     if (publish) {   // the next batch borrows the limited polynomials of this one (limiter/reconstruct.hpp:41-51)
@@ -1144,6 +1144,7 @@ int DgmWenoBatch(mcfd_ctx *ctx, double *u, double w0, double eps, int64_t taylor
   static bool configured = false;
   if (!configured) {
     MCFD_CUDA(ctx, cudaFuncSetAttribute(WenoLazyKernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    MCFD_CUDA(ctx, cudaFuncSetAttribute(WenoLazyKernel<Q>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     configured = true;
   }
   if (int s = LaunchDgmTaylor(ctx, u, taylor_begin, taylor_end)) return s;
@@ -1155,7 +1156,7 @@ int DgmWenoBatch(mcfd_ctx *ctx, double *u, double w0, double eps, int64_t taylor
   a.comp_stride = 1; a.mode_stride = 5; a.modal_state = 1; a.legendre = 1;
   (void)M;
   const int t0 = (int)(cell_begin / kTile), t1 = (int)((cell_end + kTile - 1) / kTile);
-  WenoLazyKernel<Q><<<t1 - t0, 160, smem, ctx->stream>>>(a, t0);
+  WenoLazyKernel<Q><<<t1 - t0, 160, WenoShape<Q>::kLazySharedBytes, ctx->stream>>>(a, t0);
   MCFD_CUDA(ctx, cudaGetLastError());
   ctx->launches++;
   return MCFD_OK;

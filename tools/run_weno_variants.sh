@@ -1,5 +1,5 @@
 # A/B of the resident-CTA target of the limiter kernels: build_variants/lib_weno_<minb>.so copied over the library in turn
-B="python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-e2e --no-graph --limiter"
+B="python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-e2e --no-graph --limiter"   # add "--degree 3 --cells 32" for the p = 3 kernels
 cp minicfd_b200/libminicfd_b200.so /tmp/orig.so
 for f in build_variants/lib_weno_*.so; do
   v=$(basename $f .so)
