@@ -226,18 +226,21 @@ struct StageGeometry {
   static constexpr int POINTS = 6 * FQ;                   // face points per cell
   static constexpr int ITEMS = (POINTS + NW * SUB - 1) / (NW * SUB);
   static constexpr size_t kSharedBytes =
-      (size_t)(N * 15 * CPB + kGeomRows * CPB) * sizeof(double) + 6 * 8 * FQ;
+      (size_t)(N * 15 * CPB + kGeomRows * CPB) * sizeof(double) + 6 * 8 * FQ + 6 * CPB * (sizeof(int) + 1);
   static_assert(POINTS * 5 <= N * 10, "face terms must fit behind the residual rows");
   int lane, warp, lc, sub, block, tile, tl, cell;
   bool active;
   double *sF, *sR, *sC, *sG;
-  unsigned char *sNbrNode;
+  unsigned char *sNbrNode, *sCode;
+  int *sNbr;
   MCFD_HD StageGeometry(const StageArgs &p, int tid, int bid, double *smem) {
     sF = smem;                                      // [N][15][CPB]
     sR = smem;                                      // [N][5][CPB]        (after B1)
     sC = smem + N * 5 * CPB;                        // [POINTS][5][CPB]   (after B1)
     sG = smem + N * 15 * CPB;                       // [21][CPB]
     sNbrNode = reinterpret_cast<unsigned char *>(sG + kGeomRows * CPB);  // [6][8][FQ]
+    sNbr = reinterpret_cast<int *>(sNbrNode + 6 * 8 * FQ);               // [6][CPB] neighbour of the block's cells
+    sCode = reinterpret_cast<unsigned char *>(sNbr + 6 * CPB);           // [6][CPB]
     lane = tid & 31; warp = tid >> 5;
     lc = lane % CPB;                                // cell within the block
     sub = lane / CPB;
@@ -500,6 +503,12 @@ MCFD_HD void StagePrologue(const StageArgs &p, int tid, int bid, double *smem) {
     int row = i / CPB, c = i % CPB;
     g.sG[i] = p.geom[((size_t)g.tile * kGeomRows + row) * kTile + (g.block % g.SUB) * CPB + c];
   }
+  // the face tables too: a face point's neighbour state is then one global latency away, not two
+  for (int i = tid; i < 6 * CPB; i += NW * 32) {
+    const size_t at = ((size_t)g.tile * 6 + i / CPB) * kTile + (g.block % g.SUB) * CPB + i % CPB;
+    g.sNbr[i] = p.nbr[at];
+    g.sCode[i] = p.code[at];
+  }
 }
 
 // ---- phase A: contravariant fluxes Fhat = F(u) J* at every node -> shared memory --------------
@@ -649,8 +658,8 @@ MCFD_HD void LoadPoint(const StageArgs &p, const StageGeometry<Q, CPB, NW> &g, i
   const double *uin = p.u_in + (size_t)g.tile * F * kTile + g.tl;
 #pragma unroll
   for (int c = 0; c < 5; ++c) ld->u[c] = uin[(n * 5 + c) * kTile];
-  ld->nb = p.nbr[((size_t)g.tile * 6 + f) * kTile + g.tl];
-  ld->code = p.code[((size_t)g.tile * 6 + f) * kTile + g.tl];
+  ld->nb = g.sNbr[f * CPB + g.lc];
+  ld->code = g.sCode[f * CPB + g.lc];
   if (ld->nb >= 0) {
     const int n2 = g.sNbrNode[((ld->code & 7) * 8 + ((ld->code >> 3) & 7)) * FQ + q];
     const double *src = p.u_in + ((size_t)(ld->nb >> 5) * F + n2 * 5) * kTile + (ld->nb & 31);
