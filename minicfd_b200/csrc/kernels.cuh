@@ -123,6 +123,7 @@ struct StageArgs {
   const double *h2s;            // [tile][face*3 + x][lane]         Face::HolderToSharer of my face f
   const double *cell_nu;        // [tile][comp][lane] kDiffIsotropic: viscosity of every component, per cell
   Viscosity vis;
+  const unsigned char *line_bytes;   // LineStageKernel only: LineTableBytes() in device memory
 };
 
 // diffusive part of the Riemann type, a template parameter of the stage kernel
@@ -2218,4 +2219,7 @@ __global__ void RiemannKernel(int bc_kind, int n, const double *normals, const d
 #endif  // __CUDACC__
 
 }  // namespace mcfd
+
+#include "stage_lines.cuh"
+
 #endif  // MINICFD_B200_KERNELS_CUH_

@@ -48,6 +48,9 @@ struct mcfd_ctx {
   cudaStream_t stream = nullptr;
   std::string error;
   Tables tables{};
+  LineTables line_tables{};                     // the node-line kernel's share of `tables`, a kernel parameter
+  DevBuf<unsigned char> line_bytes;             // its byte tables once more, in device memory (staged by cp.async)
+  bool use_lines = false;                       // inviscid lumped Lobatto schemes: LineStageKernel (stage_lines.cuh)
   HostMesh mesh;
   bool has_mesh = false;
   int64_t n_cells = 0, n_tiles = 0;
@@ -144,6 +147,29 @@ cudaError_t LaunchStageG(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
   }
   kernel<<<n_blocks, NW * 32, smem, ctx->stream>>>(a);
   return cudaGetLastError();
+}
+
+// The node-line kernel (stage_lines.cuh): inviscid fr::Lobatto / dg::Lobatto.  Its tables are a kernel parameter.
+template <int Q, int R, int CPB>
+cudaError_t LaunchLineR(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
+  using S = LineShape<Q, CPB>;
+  auto kernel = LineStageKernel<Q, R, CPB>;
+  // per device, not per process: the attribute belongs to the current device's copy of the function
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::kSharedBytes);
+  if (e != cudaSuccess) return e;
+  // all of the SM's shared memory: the default carve-out holds one CTA of this size, the kernel is built for kMinBlocks
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  if (e != cudaSuccess) return e;
+  kernel<<<n_blocks, S::kThreads, S::kSharedBytes, ctx->stream>>>(a, ctx->line_tables);
+  return cudaGetLastError();
+}
+template <int Q, int CPB>
+cudaError_t LaunchLine(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
+  switch (ctx->cfg.riemann) {
+  case MCFD_EXACT: return LaunchLineR<Q, kExact, CPB>(ctx, a, n_blocks);
+  case MCFD_HLLC: return LaunchLineR<Q, kHllc, CPB>(ctx, a, n_blocks);
+  default: return LaunchLineR<Q, kAusm, CPB>(ctx, a, n_blocks);
+  }
 }
 
 // the general Vincent correction (fr::General) is a separate instantiation: the lumped schemes pay nothing
@@ -260,8 +286,9 @@ int LaunchStage(mcfd_ctx *ctx, const double *u_in, const double *u0, double *u_o
   a.block_begin = (int)block_begin;
   a.mode = mode; a.dt = dt; a.dt_dev = ctx->rk_order ? ctx->rk_dt_dev : nullptr;
   a.grad = ctx->grad.p; a.hn = ctx->hn.p; a.h2s = ctx->h2s.p; a.vis = ctx->vis; a.cell_nu = ctx->cell_nu.p;
+  a.line_bytes = ctx->line_bytes.p;
   int n_blocks = (int)(block_end - block_begin);
-  MCFD_CUDA(ctx, EnsureTables(ctx));
+  if (!ctx->use_lines) MCFD_CUDA(ctx, EnsureTables(ctx));
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (ctx->timing) {
     if (ctx->events_used == ctx->events.size()) {
@@ -289,6 +316,8 @@ int LaunchStage(mcfd_ctx *ctx, const double *u_in, const double *u0, double *u_o
   } else if (ctx->cfg.diffusion != MCFD_INVISCID) {
     e = (ctx->q == 3) ? LaunchStageViscous<3, kP2ViscousCells, kP2ViscousWarps>(ctx, a, n_blocks)
                       : LaunchStageViscous<4, kP3ViscousCells, kP3ViscousWarps>(ctx, a, n_blocks);
+  } else if (ctx->use_lines) {
+    e = (ctx->q == 3) ? LaunchLine<3, kLineP2Cells>(ctx, a, n_blocks) : LaunchLine<4, kLineP3Cells>(ctx, a, n_blocks);
   } else {
     e = (ctx->q == 3) ? LaunchStageQ<3, kP2Cells, kP2Warps>(ctx, a, n_blocks)
                       : LaunchStageQ<4, kP3Cells, kP3Warps>(ctx, a, n_blocks);
@@ -435,6 +464,16 @@ int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
   ctx->cpb = (config->scheme == MCFD_DG_GENERAL) ? kTile : ((ctx->q == 3) ? (viscous ? kP2ViscousCells : kP2Cells) : (viscous ? kP3ViscousCells : kP3Cells));
   ctx->n_warps = (ctx->q == 3) ? (viscous ? kP2ViscousWarps : kP2Warps) : (viscous ? kP3ViscousWarps : kP3Warps);
   ctx->tables = BuildTables(config->degree, config->scheme, ctx->n_warps, kTile / ctx->cpb, config->fr_c_next);
+  ctx->use_lines = !viscous && ctx->q == 3 && (config->scheme == MCFD_FR_LOBATTO || config->scheme == MCFD_DG_LOBATTO);
+  if (ctx->use_lines) {
+    ctx->cpb = (ctx->q == 3) ? kLineP2Cells : kLineP3Cells;
+    ctx->n_warps = (ctx->q == 3) ? LineShape<3, kLineP2Cells>::NW : LineShape<4, kLineP3Cells>::NW;
+    ctx->line_tables = MakeLineTables(ctx->tables, ctx->q, kTile / ctx->cpb);
+    const std::vector<unsigned char> bytes = LineTableBytes(ctx->line_tables, ctx->q);
+    e = ctx->line_bytes.Alloc(bytes.size());
+    if (e == cudaSuccess) e = cudaMemcpy(ctx->line_bytes.p, bytes.data(), bytes.size(), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) return Fail(nullptr, MCFD_ERR_CUDA, cudaGetErrorString(e));
+  }
   e = ctx->dt_bits.Alloc(1);
   if (e != cudaSuccess) return Fail(nullptr, MCFD_ERR_CUDA, cudaGetErrorString(e));
   *ctx_out = ctx.release();

@@ -17,7 +17,7 @@ _lib = None
 
 def build(force=False):
     deps = [SRC] + [os.path.join(HERE, "..", "minicfd_b200", "csrc", f)
-                    for f in ("kernels.cuh", "physics.cuh", "tables.hpp", "format.cuh")]
+                    for f in ("kernels.cuh", "stage_lines.cuh", "physics.cuh", "tables.hpp", "format.cuh")]
     if force or not os.path.exists(LIB) or any(os.path.getmtime(d) > os.path.getmtime(LIB) for d in deps):
         subprocess.check_call(["g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-ffp-contract=off",
                                "-o", LIB, SRC])
@@ -45,7 +45,7 @@ def _i32(a):
 
 def stage(mesh, degree, scheme, riemann, column_in, *, n_local=None, n_ghost=0, tag_kinds=None,
           bvals=None, column_u0=None, mode=0, dt=0.0, cells=None, bfaces=None, btags=None, c_next=0.0,
-          viscous=None, cell_nu=None):
+          viscous=None, cell_nu=None, line_cells=-1):
     cells = np.ascontiguousarray(mesh.cells if cells is None else cells, dtype=np.int64)
     bfaces = np.ascontiguousarray(mesh.bfaces if bfaces is None else bfaces, dtype=np.int64)
     btags = np.ascontiguousarray(mesh.btags if btags is None else btags, dtype=np.int32)
@@ -72,7 +72,8 @@ def stage(mesh, degree, scheme, riemann, column_in, *, n_local=None, n_ghost=0, 
                          C.c_double(c_next),
                          None if viscous is None else _dp(np.ascontiguousarray(
                              (list(viscous) + [0.0])[:5], dtype=np.float64)),
-                         None if cell_nu is None else _dp(np.ascontiguousarray(cell_nu, dtype=np.float64)))
+                         None if cell_nu is None else _dp(np.ascontiguousarray(cell_nu, dtype=np.float64)),
+                         C.c_int(line_cells))
     if rc != 0:
         raise RuntimeError(err.value.decode())
     return out

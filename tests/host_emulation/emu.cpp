@@ -29,6 +29,22 @@ void RunStage(StageArgs a, int n_blocks) {
   }
 }
 
+// the node-line kernel of the lumped inviscid schemes (stage_lines.cuh), block by block
+template <int Q, int CPB>
+void RunLineStage(int riemann, StageArgs a, int64_t n_local) {
+  using S = LineShape<Q, CPB>;
+  std::vector<double> smem(S::kSharedBytes / sizeof(double) + 1);
+  const LineTables tab = MakeLineTables(c_tab, Q, kTile / CPB);
+  const std::vector<unsigned char> bytes = LineTableBytes(tab, Q);
+  a.line_bytes = bytes.data();
+  const int n_blocks = (int)((n_local + CPB - 1) / CPB);
+  for (int b = 0; b < n_blocks; ++b) {
+    if (riemann == 0) RunLineStageBlockOnHost<Q, kExact, CPB>(a, tab, b, smem.data());
+    else if (riemann == 1) RunLineStageBlockOnHost<Q, kHllc, CPB>(a, tab, b, smem.data());
+    else RunLineStageBlockOnHost<Q, kAusm, CPB>(a, tab, b, smem.data());
+  }
+}
+
 template <int Q, int CPB, int NW>
 void RunStageQ(int riemann, StageArgs a, int n_blocks) {
   if (riemann == 0) RunStage<Q, kExact, CPB, NW>(a, n_blocks);
@@ -57,8 +73,11 @@ int emu_stage(int degree, int scheme, int riemann, int64_t n_nodes, const double
     const int32_t *tag_kinds, const double *bvals, const double *column_in, const double *column_u0,
     int mode, double dt, double *column_out, char *err, int err_len, double c_next,
     const double *viscous /* null, or beta0, beta1, nu, prandtl, kLocal (0 / 1: the traces interpolate det u) */,
-    const double *cell_nu /* null, or [n_cells][5]: the component-wise isotropic model */) {
+    const double *cell_nu /* null, or [n_cells][5]: the component-wise isotropic model */,
+    int line_cells /* 0: the slot kernel (StageKernel); 16 | 32: the node-line kernel with that many cells per block;
+                      -1: the library's choice */) {
   const int q = degree + 1, F = 5 * q * q * q;
+  if (line_cells < 0) line_cells = q == 3 ? kLineP2Cells : 0;   // degree 3 stays on the slot kernel
   const int cpb = (q == 3) ? kP2Cells : kP3Cells, nw = (q == 3) ? kP2Warps : kP3Warps;
   c_tab = BuildTables(degree, scheme, nw, kTile / cpb, c_next);
   HostMesh mesh;
@@ -106,7 +125,13 @@ int emu_stage(int degree, int scheme, int riemann, int64_t n_nodes, const double
     a.vis.cond = viscous[2] * (kGasR * kGammaOverGm1) / viscous[3];
   }
   int n_blocks = (int)((n_local + cpb - 1) / cpb);
-  if (q == 3) RunStageQ<3, kP2Cells, kP2Warps>(riemann, a, n_blocks);
+  const bool lines = !viscous && scheme != 2 && line_cells != 0;   // what LaunchStage of the library picks
+  if (lines && q == 3 && line_cells == 16) RunLineStage<3, 16>(riemann, a, n_local);
+  else if (lines && q == 3) RunLineStage<3, 32>(riemann, a, n_local);
+  else if (lines && line_cells == 32) RunLineStage<4, 32>(riemann, a, n_local);
+  else if (lines && line_cells == 8) RunLineStage<4, 8>(riemann, a, n_local);
+  else if (lines) RunLineStage<4, 16>(riemann, a, n_local);
+  else if (q == 3) RunStageQ<3, kP2Cells, kP2Warps>(riemann, a, n_blocks);
   else RunStageQ<4, kP3Cells, kP3Warps>(riemann, a, n_blocks);
   for (int64_t c = 0; c < n_local; ++c)
     for (int f = 0; f < F; ++f) column_out[c * F + f] = uout[((c >> 5) * F + f) * kTile + (c & 31)];
