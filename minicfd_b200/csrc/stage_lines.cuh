@@ -394,7 +394,9 @@ MCFD_HD void LinePhaseA(const StageArgs &p, const LineTables &tab, int tid, int 
     double r0[3], r1[3], s[3];
 #pragma unroll
     for (int x = 0; x < 3; ++x) { r0[x] = fma(z, J.B0[x], J.A0[x]); r1[x] = fma(z, J.B1[x], J.A1[x]); }
-    const PrimA q = ConsToPrimA(t->u[k]);
+    bool ok;
+    PrimA q = ConsToPrimFlat(t->u[k], &ok);       // branch-free: the Q nodes of the line are Q independent streams
+    if (!ok) q = ConsToPrimA(t->u[k]);             // clipped or vacuum state
     double *dk = dst + k * ND * CPB;
     dk[15 * CPB] = q.rho; dk[16 * CPB] = q.u; dk[17 * CPB] = q.v; dk[18 * CPB] = q.w; dk[19 * CPB] = q.p; dk[20 * CPB] = q.a;
     double f[5];
@@ -514,19 +516,19 @@ MCFD_HD PointSetup LinePointSetup(const LineTables &tab, const LineThread<Q, CPB
   return s;
 }
 
-// ---- phase B: face points two at a time, then node by node the rest of the divergence, 1/det, the update ------
+// ---- phase F: the face points of the line, two at a time.  Touches only what this thread wrote in phase A and
+// its own staged neighbour states, so no barrier separates the two.
 template <int Q, int kRiemann, int CPB>
-MCFD_HD void LinePhaseB(const StageArgs &p, const LineTables &tab, int tid, int bid, double *smem) {
+MCFD_HD void LinePhaseF(const StageArgs &p, const LineTables &tab, int tid, int bid, double *smem) {
   using S = LineShape<Q, CPB>;
   constexpr int FQ = S::FQ, ND = S::kNodeDoubles;
   LineThread<Q, CPB> g(p, tab, tid, bid, smem);
   if (!g.valid || !g.active) return;
   const int i = g.i, j = g.j, lc = g.lc;
-  const bool i_end = i == 0 || i == Q - 1, j_end = j == 0 || j == Q - 1;
   const int n0 = (i * Q + j) * Q;
   double *own = g.sF + (size_t)n0 * ND * CPB + lc;       // this line's nodes
   const LineJacobian J = ComputeLineJacobian(g.sG + lc, CPB, tab.xi[i], tab.xi[j]);
-  // ---- face points.  Each pass solves two of them in straight-line code — two independent dependency chains per
+  // Each pass solves two of them in straight-line code — two independent dependency chains per
   // warp — and adds the lifted terms to the accumulators of their nodes in shared memory.
   const int n_pairs = tab.cls_pairs[g.cls];
 #pragma unroll 1
@@ -571,8 +573,41 @@ MCFD_HD void LinePhaseB(const StageArgs &p, const LineTables &tab, int tid, int 
 #pragma unroll
     for (int c = 0; c < 5; ++c) acc_b[c * CPB] = fma(scb, fb[c], acc_b[c * CPB]);
   }
-  // ---- nodes: xi and eta parts of the divergence, 1/det (fr/general.hpp:256-266; dg/lobatto.hpp:143-158),
-  // RK update (rk.hpp:16-56), store
+}
+
+// ---- phase N, behind the barrier that publishes F^_xi and F^_eta: per node the xi and eta parts of the divergence,
+// 1/det (fr/general.hpp:256-266; dg/lobatto.hpp:143-158), RK update (rk.hpp:16-56), store.  Its global loads are
+// issued before the barrier.
+template <int Q, int CPB>
+struct LineUpdateLoads {
+  double uo[Q][5], u0[Q][5];
+};
+template <int Q, int CPB>
+MCFD_HD void LineLoadUpdate(const StageArgs &p, const LineTables &tab, int tid, int bid, double *smem, LineUpdateLoads<Q, CPB> *ld) {
+  using S = LineShape<Q, CPB>;
+  LineThread<Q, CPB> g(p, tab, tid, bid, smem);
+  if (!g.valid || !g.active) return;
+  const size_t row0 = (size_t)g.tile * S::F * kTile + (size_t)((g.i * Q + g.j) * Q) * 5 * kTile + g.tl;
+#pragma unroll
+  for (int k = 0; k < Q; ++k) {
+#pragma unroll
+    for (int c = 0; c < 5; ++c) {
+      ld->uo[k][c] = p.u_in[row0 + (k * 5 + c) * kTile];
+      ld->u0[k][c] = p.mode >= kModeRk3b ? p.u0[row0 + (k * 5 + c) * kTile] : 0.0;
+    }
+  }
+}
+template <int Q, int CPB>
+MCFD_HD void LinePhaseN(const StageArgs &p, const LineTables &tab, int tid, int bid, double *smem, const LineUpdateLoads<Q, CPB> &ld) {
+  using S = LineShape<Q, CPB>;
+  constexpr int FQ = S::FQ, ND = S::kNodeDoubles;
+  LineThread<Q, CPB> g(p, tab, tid, bid, smem);
+  if (!g.valid || !g.active) return;
+  const int i = g.i, j = g.j, lc = g.lc;
+  const bool i_end = i == 0 || i == Q - 1, j_end = j == 0 || j == Q - 1;
+  const int n0 = (i * Q + j) * Q;
+  const double *own = g.sF + (size_t)n0 * ND * CPB + lc;
+  const LineJacobian J = ComputeLineJacobian(g.sG + lc, CPB, tab.xi[i], tab.xi[j]);
   const double cF = tab.coef_F;
   double a0[Q], a1[Q];
 #pragma unroll
@@ -585,15 +620,11 @@ MCFD_HD void LinePhaseB(const StageArgs &p, const LineTables &tab, int tid, int 
   const size_t row0 = (size_t)g.tile * S::F * kTile + (size_t)n0 * 5 * kTile + g.tl;
   const double dt = p.dt_dev ? *p.dt_dev : p.dt;
   const int mode = p.mode;
-  double uo[Q][5], u0[Q][5];     // one round trip for the whole line
-#pragma unroll
-  for (int k = 0; k < Q; ++k) {
-#pragma unroll
-    for (int c = 0; c < 5; ++c) {
-      uo[k][c] = p.u_in[row0 + (k * 5 + c) * kTile];
-      u0[k][c] = mode >= kModeRk3b ? p.u0[row0 + (k * 5 + c) * kTile] : 0.0;
-    }
-  }
+  // kModeEuler: w;  kModeRk3b: (u0 3 + w) / 4;  kModeRk3c: (w 2 + u0) / 3;  kModeRk2b: (w + u0) / 2
+  const double cw = mode == kModeRk3c ? 2.0 : 1.0;
+  const double c0 = mode == kModeRk3b ? 3.0 : (mode == kModeRk3c || mode == kModeRk2b ? 1.0 : 0.0);
+  const double cs_inv = mode == kModeRk3b ? 4.0 : (mode == kModeRk3c ? 3.0 : (mode == kModeRk2b ? 2.0 : 1.0));
+  const double cs = mode == kModeRk3b ? 0.25 : (mode == kModeRk3c ? 1.0 / 3 : (mode == kModeRk2b ? 0.5 : 1.0));
 #pragma unroll
   for (int k = 0; k < Q; ++k) {
     double r[5];
@@ -617,17 +648,13 @@ MCFD_HD void LinePhaseB(const StageArgs &p, const LineTables &tab, int tid, int 
 #pragma unroll
     for (int c = 0; c < 5; ++c) {
       const double res = r[c] * inv_det;
-      const double w = fma(res, dt, uo[k][c]);
-      double val;
-      if (mode == kModeResidual) val = res;
-      else if (mode == kModeEuler) val = w;
-      else if (mode == kModeRk3b) val = (u0[k][c] * 3 + w) * 0.25;
-      else if (mode == kModeRk3c) {
-        const double s = w * 2 + u0[k][c];            // s / 3, correctly rounded in all but rare half-way cases
-        const double qv = s * (1.0 / 3);
-        val = fma(fma(-3.0, qv, s), 1.0 / 3, qv);
-      } else val = (w + u0[k][c]) * 0.5;
-      p.u_out[row0 + (k * 5 + c) * kTile] = val;
+      const double w = fma(res, dt, ld.uo[k][c]);
+      // (w cw + u0 c0) cs with cs = 1, 1/4, 1/3, 1/2 (rk.hpp:16-49); the last two operations make the quotient by 3
+      // correctly rounded in all but rare half-way cases and change nothing for the powers of two
+      const double sum = fma(ld.u0[k][c], c0, w * cw);
+      const double qv = sum * cs;
+      const double val = fma(fma(-cs_inv, qv, sum), cs, qv);
+      p.u_out[row0 + (k * 5 + c) * kTile] = mode == kModeResidual ? res : val;
     }
   }
 }
@@ -644,8 +671,11 @@ LineStageKernel(const __grid_constant__ StageArgs p, const __grid_constant__ Lin
   AsyncCopyWait();
   __syncthreads();
   LinePhaseA<Q, CPB>(p, tab, tid, bid, smem, &t);
+  LinePhaseF<Q, kRiemann, CPB>(p, tab, tid, bid, smem);
+  LineUpdateLoads<Q, CPB> ld;
+  LineLoadUpdate<Q, CPB>(p, tab, tid, bid, smem, &ld);    // in flight across the barrier
   __syncthreads();
-  LinePhaseB<Q, kRiemann, CPB>(p, tab, tid, bid, smem);
+  LinePhaseN<Q, CPB>(p, tab, tid, bid, smem, ld);
 }
 #else
 template <int Q, int kRiemann, int CPB>
@@ -656,8 +686,13 @@ void RunLineStageBlockOnHost(const StageArgs &p, const LineTables &tab, int bid,
     LineLoad<Q, CPB>(p, tab, t, bid, smem, &regs[t]);
     LinePrologue<Q, CPB>(p, tab, t, bid, smem);
   }
-  for (int t = 0; t < T; ++t) LinePhaseA<Q, CPB>(p, tab, t, bid, smem, &regs[t]);
-  for (int t = 0; t < T; ++t) LinePhaseB<Q, kRiemann, CPB>(p, tab, t, bid, smem);
+  static LineUpdateLoads<Q, CPB> ld[T];
+  for (int t = 0; t < T; ++t) {
+    LinePhaseA<Q, CPB>(p, tab, t, bid, smem, &regs[t]);
+    LinePhaseF<Q, kRiemann, CPB>(p, tab, t, bid, smem);
+    LineLoadUpdate<Q, CPB>(p, tab, t, bid, smem, &ld[t]);
+  }
+  for (int t = 0; t < T; ++t) LinePhaseN<Q, CPB>(p, tab, t, bid, smem, ld[t]);
 }
 #endif
 
