@@ -99,6 +99,16 @@ SYMBOLS = {
     "mcfd_enable_kernel_timing": (C.c_int, [_P, C.c_int]),
     "mcfd_kernel_time": (C.c_int, [_P, _D, _I64, C.c_int]),
     "mcfd_riemann_flux": (C.c_int, [_P, C.c_int32, C.c_int64, _D, _D, _D, _D]),
+    "mcfd_peer_export": (C.c_int, [_P, C.c_int32, _P, C.POINTER(_P)]),
+    "mcfd_peer_open": (C.c_int, [_P, _P, C.POINTER(_P)]),
+    "mcfd_peer_connect": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, C.POINTER(_P), C.POINTER(_P), _I32, _I64,
+                                    C.POINTER(_P), C.POINTER(_P)]),
+    "mcfd_peer_push": (C.c_int, [_P]),
+    "mcfd_peer_wait": (C.c_int, [_P]),
+    "mcfd_peer_min_time_step": (C.c_int, [_P, _P]),
+    "mcfd_peer_step": (C.c_int, [_P, C.c_int, C.c_double, C.c_double]),
+    "mcfd_peer_step_group": (C.c_int, [C.POINTER(_P), C.c_int32, C.c_int, C.c_double, C.c_double]),
+    "mcfd_peer_check": (C.c_int, [_P]),
 }
 
 
@@ -138,6 +148,15 @@ def time_step_static(scheme, degree, n_cells, column_ptr, length_ptr, dt_guess, 
                                    _P(dt_ptr), _P(stream))
     if rc != 0:
         raise McfdError(f"libminicfd_b200 error {rc}: {lib.mcfd_last_error(None).decode()}")
+
+
+def peer_step_group(contexts, order, t, dt_guess):
+    """mcfd_peer_step_group: the contexts of this process advance one step in lockstep."""
+    lib = load()
+    arr = (_P * len(contexts))(*[c.h for c in contexts])
+    rc = lib.mcfd_peer_step_group(arr, len(contexts), order, t, dt_guess)
+    if rc != 0:
+        raise McfdError(f"libminicfd_b200 error {rc}: " + "; ".join(lib.mcfd_last_error(c.h).decode() for c in contexts))
 
 
 class Context:
@@ -310,6 +329,47 @@ class Context:
         sn, rn = C.c_int64(), C.c_int64()
         self._check(self.lib.mcfd_halo_buffers(self.h, C.byref(sp), C.byref(sn), C.byref(rp), C.byref(rn)))
         return (sp.value or 0, sn.value), (rp.value or 0, rn.value)
+
+    # ---- halo through peer-mapped memory (mcfd_peer_*) ----
+    def peer_export(self, world):
+        """-> (five 64-byte IPC handles, five device pointers): state buffers 0..2, epoch words, dt slots."""
+        handles = (C.c_ubyte * (5 * 64))()
+        ptrs = (_P * 5)()
+        self._check(self.lib.mcfd_peer_export(self.h, world, C.cast(handles, _P), ptrs))
+        raw = bytes(handles)
+        return [raw[64 * i:64 * (i + 1)] for i in range(5)], [p or 0 for p in ptrs]
+
+    def peer_open(self, handle: bytes) -> int:
+        buf = (C.c_ubyte * 64).from_buffer_copy(handle)
+        out = _P()
+        self._check(self.lib.mcfd_peer_open(self.h, C.cast(buf, _P), C.byref(out)))
+        return out.value
+
+    def peer_connect(self, rank, world, neighbour_state, neighbour_flags, slot_at_neighbour, dest_cells, world_flags,
+                     world_dt_slots):
+        n = len(neighbour_flags)
+        st = (_P * max(1, 3 * n))(*[p for trio in neighbour_state for p in trio])
+        fl = (_P * max(1, n))(*neighbour_flags)
+        slots = np.ascontiguousarray(slot_at_neighbour, dtype=np.int32)
+        dest = np.ascontiguousarray(dest_cells, dtype=np.int64)
+        wf = (_P * world)(*world_flags)
+        ws = (_P * world)(*world_dt_slots)
+        self._check(self.lib.mcfd_peer_connect(self.h, rank, world, n, st, fl, slots.ctypes.data_as(_I32), _ip(dest), wf, ws))
+
+    def peer_push(self):
+        self._check(self.lib.mcfd_peer_push(self.h))
+
+    def peer_wait(self):
+        self._check(self.lib.mcfd_peer_wait(self.h))
+
+    def peer_min_time_step(self, dt_ptr=0):
+        self._check(self.lib.mcfd_peer_min_time_step(self.h, _P(dt_ptr)))
+
+    def peer_step(self, order, t, dt_guess):
+        self._check(self.lib.mcfd_peer_step(self.h, order, t, dt_guess))
+
+    def peer_check(self):
+        self._check(self.lib.mcfd_peer_check(self.h))
 
     def halo_pack(self):
         self._check(self.lib.mcfd_halo_pack(self.h))

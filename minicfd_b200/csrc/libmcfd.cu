@@ -11,6 +11,7 @@
 
 #include "../../include/minicfd_b200.h"
 #include "kernels.cuh"
+#include "peer.cuh"
 #include "format.cuh"
 #include "shuffle.cuh"
 #include "tables.hpp"
@@ -80,6 +81,7 @@ struct mcfd_ctx {
   Viscosity vis{2.0, 1.0 / 12, 0.0, 0.0};       // Direct::SetBetaValues / NavierStokes::SetProperty
   double prandtl = 0.708;
   DevBuf<int> nbr, send_cells, recv_cells;
+  std::vector<int64_t> send_counts;             // per neighbour, in list order (mcfd_set_halo)
   DevBuf<unsigned char> code, bkind;
   DevBuf<double> send_buf, recv_buf;
   DevBuf<unsigned long long> dt_bits;
@@ -97,6 +99,25 @@ struct mcfd_ctx {
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> events;
   size_t events_used = 0;
   int64_t inner_blocks = 0, total_blocks = 0;  // CTA-sized blocks without / with ghost neighbours
+  // ---- halo through peer-mapped memory (mcfd_peer_*): the send cells' rows go straight into the neighbours' ghost rows
+  struct Peer {
+    bool connected = false;
+    int n_neighbours = 0, rank = 0, world = 1;
+    DevBuf<unsigned long long> flags;            // [kPeerWords]: halo epochs per neighbour slot, then dt epochs per rank
+    DevBuf<double> dt_slots;                     // [2][world]: every rank's time step, by step parity
+    DevBuf<int> dest_cells;                      // ghost cell id at the neighbour, per send item
+    DevBuf<int> item_neighbour;                  // neighbour slot, per send item
+    DevBuf<double *> state_dev;                  // [n_neighbours][3] the neighbours' state buffers
+    DevBuf<unsigned long long *> flag_dev;       // [n_neighbours] the word to signal at each neighbour
+    DevBuf<double *> dt_slot_dev;                // [world] every rank's dt_slots
+    DevBuf<unsigned long long *> dt_flag_dev;    // [world] every rank's dt epoch word for this rank
+    DevBuf<unsigned int> done;                   // block counter of the push kernel
+    DevBuf<int> error;                           // set when a wait gave up
+    std::vector<void *> opened;                  // cudaIpcOpenMemHandle results
+    unsigned long long halo_epoch = 0, dt_epoch = 0;
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_main = nullptr, ev_side = nullptr;
+  } peer;
 };
 
 namespace {
@@ -484,6 +505,10 @@ int mcfd_destroy(mcfd_ctx *ctx) {
   if (!ctx) return MCFD_OK;
   for (auto &p : ctx->events) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
   if (ctx->trace_done) cudaEventDestroy(ctx->trace_done);
+  for (void *p : ctx->peer.opened) cudaIpcCloseMemHandle(p);
+  if (ctx->peer.ev_main) cudaEventDestroy(ctx->peer.ev_main);
+  if (ctx->peer.ev_side) cudaEventDestroy(ctx->peer.ev_side);
+  if (ctx->peer.side) cudaStreamDestroy(ctx->peer.side);
   delete ctx;
   return MCFD_OK;
 }
@@ -631,6 +656,8 @@ int mcfd_set_halo(mcfd_ctx *ctx, int32_t n_send_parts, const int64_t *send_count
       return Fail(ctx, MCFD_ERR_ARG, "recv cell is not a ghost cell");
     r32[i] = (int)recv_cells[i];
   }
+  ctx->send_counts.assign(send_counts, send_counts + n_send_parts);
+  ctx->peer.connected = false;
   MCFD_CUDA(ctx, ctx->send_cells.Alloc(ns));
   MCFD_CUDA(ctx, ctx->recv_cells.Alloc(nr));
   MCFD_CUDA(ctx, ctx->send_buf.Alloc(ns * ctx->fields));
@@ -1100,6 +1127,238 @@ int mcfd_rk_step_device(mcfd_ctx *ctx, int order, double t, const double *dt_dev
     if (int s = mcfd_rk_stage_inner(ctx, stage)) { ctx->rk_order = 0; return s; }
     if (int s = mcfd_rk_stage_inter(ctx, stage)) { ctx->rk_order = 0; return s; }
   }
+  return MCFD_OK;
+}
+
+// ---- halo and time-step minimum through peer-mapped memory (peer.cuh) -------------------------------------------
+
+int mcfd_peer_export(mcfd_ctx *ctx, int32_t world, mcfd_ipc_handle *handles, void **pointers) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (world < 1 || world > kPeerMaxRanks) return Fail(ctx, MCFD_ERR_ARG, "world size must be 1..64");
+  auto &pe = ctx->peer;
+  pe.world = world;
+  MCFD_CUDA(ctx, pe.flags.Alloc(kPeerWords));
+  MCFD_CUDA(ctx, cudaMemset(pe.flags.p, 0, kPeerWords * sizeof(unsigned long long)));
+  MCFD_CUDA(ctx, pe.dt_slots.Alloc(2 * (size_t)world));
+  MCFD_CUDA(ctx, cudaMemset(pe.dt_slots.p, 0, 2 * (size_t)world * sizeof(double)));
+  pe.halo_epoch = pe.dt_epoch = 0;
+  pe.connected = false;
+  void *ptrs[5] = {ctx->u[0].p, ctx->u[1].p, ctx->u[2].p, pe.flags.p, pe.dt_slots.p};
+  for (int i = 0; i < 5; ++i) {
+    if (pointers) pointers[i] = ptrs[i];
+    if (handles) {
+      static_assert(sizeof(cudaIpcMemHandle_t) == sizeof(mcfd_ipc_handle), "handle size");
+      cudaIpcMemHandle_t h;
+      MCFD_CUDA(ctx, cudaIpcGetMemHandle(&h, ptrs[i]));
+      std::memcpy(handles[i].bytes, &h, sizeof(h));
+    }
+  }
+  return MCFD_OK;
+}
+
+int mcfd_peer_open(mcfd_ctx *ctx, const mcfd_ipc_handle *handle, void **pointer) {
+  if (!ctx || !handle || !pointer) return Fail(ctx, MCFD_ERR_ARG, "null argument");
+  cudaIpcMemHandle_t h;
+  std::memcpy(&h, handle->bytes, sizeof(h));
+  void *p = nullptr;
+  MCFD_CUDA(ctx, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+  ctx->peer.opened.push_back(p);
+  *pointer = p;
+  return MCFD_OK;
+}
+
+int mcfd_peer_connect(mcfd_ctx *ctx, int32_t rank, int32_t world, int32_t n_neighbours, void *const *neighbour_state,
+    void *const *neighbour_flags, const int32_t *slot_at_neighbour, const int64_t *dest_cells, void *const *world_flags,
+    void *const *world_dt_slots) {
+  if (int s = RequireMesh(ctx)) return s;
+  auto &pe = ctx->peer;
+  if (!pe.flags.p || world != pe.world) return Fail(ctx, MCFD_ERR_STATE, "call mcfd_peer_export with this world size first");
+  if (rank < 0 || rank >= world || n_neighbours < 0 || n_neighbours > kPeerMaxNeighbours ||
+      n_neighbours != (int)ctx->send_counts.size())
+    return Fail(ctx, MCFD_ERR_ARG, "rank / neighbour count does not match mcfd_set_halo");
+  if (!world_flags || !world_dt_slots || (n_neighbours && (!neighbour_state || !neighbour_flags || !slot_at_neighbour || !dest_cells)))
+    return Fail(ctx, MCFD_ERR_ARG, "null argument");
+  const size_t n_items = ctx->send_cells.n;
+  std::vector<int> dest(n_items), item_nbr(n_items);
+  size_t x = 0;
+  for (int i = 0; i < n_neighbours; ++i)
+    for (int64_t k = 0; k < ctx->send_counts[i]; ++k, ++x) {
+      if (dest_cells[x] < 0 || dest_cells[x] >= ((int64_t)1 << 30)) return Fail(ctx, MCFD_ERR_ARG, "bad destination cell");
+      dest[x] = (int)dest_cells[x];
+      item_nbr[x] = i;
+    }
+  std::vector<double *> st(3 * (size_t)n_neighbours);
+  std::vector<unsigned long long *> fl(n_neighbours);
+  for (int i = 0; i < n_neighbours; ++i) {
+    if (slot_at_neighbour[i] < 0 || slot_at_neighbour[i] >= kPeerMaxNeighbours) return Fail(ctx, MCFD_ERR_ARG, "bad neighbour slot");
+    for (int b = 0; b < 3; ++b) st[3 * i + b] = static_cast<double *>(neighbour_state[3 * i + b]);
+    fl[i] = static_cast<unsigned long long *>(neighbour_flags[i]) + slot_at_neighbour[i];
+  }
+  std::vector<double *> ds(world);
+  std::vector<unsigned long long *> df(world);
+  for (int r = 0; r < world; ++r) {
+    ds[r] = static_cast<double *>(world_dt_slots[r]);
+    df[r] = static_cast<unsigned long long *>(world_flags[r]) + kPeerMaxNeighbours + rank;
+  }
+  MCFD_CUDA(ctx, pe.dest_cells.Alloc(n_items));
+  MCFD_CUDA(ctx, pe.item_neighbour.Alloc(n_items));
+  MCFD_CUDA(ctx, pe.state_dev.Alloc(st.size()));
+  MCFD_CUDA(ctx, pe.flag_dev.Alloc(fl.size()));
+  MCFD_CUDA(ctx, pe.dt_slot_dev.Alloc(world));
+  MCFD_CUDA(ctx, pe.dt_flag_dev.Alloc(world));
+  MCFD_CUDA(ctx, pe.done.Alloc(1));
+  MCFD_CUDA(ctx, pe.error.Alloc(1));
+  if (!ctx->dt_dev.p) MCFD_CUDA(ctx, ctx->dt_dev.Alloc(1));   // not inside a step: cudaMalloc may wait for kernels that poll
+  MCFD_CUDA(ctx, cudaMemset(pe.done.p, 0, sizeof(unsigned int)));
+  MCFD_CUDA(ctx, cudaMemset(pe.error.p, 0, sizeof(int)));
+  if (n_items) {
+    MCFD_CUDA(ctx, cudaMemcpy(pe.dest_cells.p, dest.data(), n_items * sizeof(int), cudaMemcpyHostToDevice));
+    MCFD_CUDA(ctx, cudaMemcpy(pe.item_neighbour.p, item_nbr.data(), n_items * sizeof(int), cudaMemcpyHostToDevice));
+  }
+  if (n_neighbours) {
+    MCFD_CUDA(ctx, cudaMemcpy(pe.state_dev.p, st.data(), st.size() * sizeof(double *), cudaMemcpyHostToDevice));
+    MCFD_CUDA(ctx, cudaMemcpy(pe.flag_dev.p, fl.data(), fl.size() * sizeof(void *), cudaMemcpyHostToDevice));
+  }
+  MCFD_CUDA(ctx, cudaMemcpy(pe.dt_slot_dev.p, ds.data(), world * sizeof(double *), cudaMemcpyHostToDevice));
+  MCFD_CUDA(ctx, cudaMemcpy(pe.dt_flag_dev.p, df.data(), world * sizeof(void *), cudaMemcpyHostToDevice));
+  if (!pe.side) {
+    int lo = 0, hi = 0;
+    MCFD_CUDA(ctx, cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    MCFD_CUDA(ctx, cudaStreamCreateWithPriority(&pe.side, cudaStreamNonBlocking, hi));
+    MCFD_CUDA(ctx, cudaEventCreateWithFlags(&pe.ev_main, cudaEventDisableTiming));
+    MCFD_CUDA(ctx, cudaEventCreateWithFlags(&pe.ev_side, cudaEventDisableTiming));
+  }
+  pe.rank = rank;
+  pe.n_neighbours = n_neighbours;
+  pe.connected = true;
+  return MCFD_OK;
+}
+
+static int RequirePeer(mcfd_ctx *ctx) {
+  if (int s = RequireMesh(ctx)) return s;
+  if (!ctx->peer.connected) return Fail(ctx, MCFD_ERR_STATE, "no peer connection (mcfd_peer_connect)");
+  return MCFD_OK;
+}
+
+int mcfd_peer_push(mcfd_ctx *ctx) {
+  if (int s = RequirePeer(ctx)) return s;
+  auto &pe = ctx->peer;
+  const int buf = ctx->rk_order ? ctx->rk_in : ctx->cur;
+  ++pe.halo_epoch;
+  const int n_items = (int)ctx->send_cells.n;
+  if (pe.n_neighbours == 0) return MCFD_OK;
+  const int threads = 128;
+  const dim3 grid((unsigned)std::max(1, (n_items + threads - 1) / threads), (unsigned)std::min(ctx->fields, 27));
+  PeerPushKernel<<<grid, threads, 0, ctx->stream>>>(ctx->u[buf].p, ctx->fields, ctx->send_cells.p, pe.dest_cells.p,
+      pe.item_neighbour.p, n_items, pe.state_dev.p, buf, pe.flag_dev.p, pe.n_neighbours, pe.halo_epoch, pe.done.p);
+  MCFD_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  return MCFD_OK;
+}
+
+int mcfd_peer_wait(mcfd_ctx *ctx) {
+  if (int s = RequirePeer(ctx)) return s;
+  auto &pe = ctx->peer;
+  if (pe.n_neighbours == 0) return MCFD_OK;
+  if (pe.halo_epoch == 0) return Fail(ctx, MCFD_ERR_STATE, "nothing has been pushed yet (mcfd_peer_push)");
+  PeerWaitKernel<<<1, kPeerMaxNeighbours, 0, ctx->stream>>>(pe.flags.p, pe.n_neighbours, pe.halo_epoch, pe.error.p);
+  MCFD_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  return MCFD_OK;
+}
+
+static int PeerDtPublish(mcfd_ctx *ctx, double *dt_dev) {
+  auto &pe = ctx->peer;
+  ++pe.dt_epoch;
+  PeerDtPublishKernel<<<1, kPeerMaxRanks, 0, ctx->stream>>>(dt_dev, pe.rank, pe.world, (int)(pe.dt_epoch & 1),
+      pe.dt_slot_dev.p, pe.dt_flag_dev.p, pe.dt_epoch);
+  MCFD_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  return MCFD_OK;
+}
+static int PeerDtReduce(mcfd_ctx *ctx, double *dt_dev) {
+  auto &pe = ctx->peer;
+  PeerDtReduceKernel<<<1, kPeerMaxRanks, 0, ctx->stream>>>(pe.flags.p + kPeerMaxNeighbours, pe.dt_slots.p, pe.world,
+      (int)(pe.dt_epoch & 1), pe.dt_epoch, dt_dev, pe.error.p);
+  MCFD_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  return MCFD_OK;
+}
+
+int mcfd_peer_min_time_step(mcfd_ctx *ctx, double *dt_dev) {
+  if (int s = RequirePeer(ctx)) return s;
+  if (!dt_dev) dt_dev = ctx->dt_dev.p;
+  if (int s = PeerDtPublish(ctx, dt_dev)) return s;
+  return PeerDtReduce(ctx, dt_dev);
+}
+
+// One stage of an open RK step: the inner cells on the caller's stream (fem.hpp:249-254) while the high-priority side
+// stream waits for the ghost rows, advances the inter cells (fem.hpp:255-256) and at once sends their new values on.
+static int PeerStage(mcfd_ctx *ctx, int stage) {
+  auto &pe = ctx->peer;
+  cudaStream_t main = ctx->stream;
+  MCFD_CUDA(ctx, cudaEventRecord(pe.ev_main, main));
+  MCFD_CUDA(ctx, cudaStreamWaitEvent(pe.side, pe.ev_main, 0));
+  if (int s = mcfd_rk_stage_inner(ctx, stage)) return s;
+  ctx->stream = pe.side;
+  int status = mcfd_peer_wait(ctx);
+  if (status == MCFD_OK) status = mcfd_rk_stage_inter(ctx, stage);
+  if (status == MCFD_OK) status = mcfd_peer_push(ctx);
+  ctx->stream = main;
+  if (status != MCFD_OK) return status;
+  MCFD_CUDA(ctx, cudaEventRecord(pe.ev_side, pe.side));
+  MCFD_CUDA(ctx, cudaStreamWaitEvent(main, pe.ev_side, 0));
+  return MCFD_OK;
+}
+
+// Several contexts driven by this thread (one per GPU, or several on one GPU) advance in lockstep: every push is
+// enqueued before any wait that depends on it, whatever streams and hardware queues the contexts share.
+int mcfd_peer_step_group(mcfd_ctx *const *ctxs, int32_t n, int order, double t, double dt_guess) {
+  if (!ctxs || n < 1) return MCFD_ERR_ARG;
+  for (int c = 0; c < n; ++c) {
+    if (int s = RequirePeer(ctxs[c])) return s;
+    if (ctxs[c]->cfg.diffusion != MCFD_INVISCID || ctxs[c]->cfg.scheme == MCFD_DG_GENERAL)
+      return Fail(ctxs[c], MCFD_ERR_ARG, "mcfd_peer_step is built for the inviscid nodal schemes");
+  }
+  int dev0 = 0;
+  cudaGetDevice(&dev0);
+  auto on = [&](mcfd_ctx *ctx) { if (ctx->cfg.device >= 0) cudaSetDevice(ctx->cfg.device); };
+  int status = MCFD_OK;
+  for (int c = 0; c < n && !status; ++c) {   // the ghost images of a solution that has never been sent
+    on(ctxs[c]);
+    if (ctxs[c]->peer.halo_epoch == 0) status = mcfd_peer_push(ctxs[c]);
+  }
+  for (int c = 0; c < n && !status; ++c) {
+    on(ctxs[c]);
+    status = mcfd_time_step_device(ctxs[c], dt_guess, order, nullptr);
+    if (!status) status = PeerDtPublish(ctxs[c], ctxs[c]->dt_dev.p);
+  }
+  for (int c = 0; c < n && !status; ++c) {
+    on(ctxs[c]);
+    status = PeerDtReduce(ctxs[c], ctxs[c]->dt_dev.p);
+    if (!status) status = mcfd_rk_begin_device(ctxs[c], order, t, ctxs[c]->dt_dev.p);
+  }
+  for (int stage = 0; stage < order && !status; ++stage)
+    for (int c = 0; c < n && !status; ++c) {
+      on(ctxs[c]);
+      status = PeerStage(ctxs[c], stage);
+    }
+  if (status) for (int c = 0; c < n; ++c) ctxs[c]->rk_order = 0;
+  cudaSetDevice(dev0);
+  return status;
+}
+
+int mcfd_peer_step(mcfd_ctx *ctx, int order, double t, double dt_guess) {
+  return mcfd_peer_step_group(&ctx, 1, order, t, dt_guess);
+}
+
+int mcfd_peer_check(mcfd_ctx *ctx) {
+  if (int s = RequirePeer(ctx)) return s;
+  MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->peer.side));
+  int err = 0;
+  MCFD_CUDA(ctx, cudaMemcpy(&err, ctx->peer.error.p, sizeof(int), cudaMemcpyDeviceToHost));
+  if (err) return Fail(ctx, MCFD_ERR_STATE, "a neighbour's data did not arrive within the polling limit");
   return MCFD_OK;
 }
 

@@ -121,7 +121,7 @@ def main():
     torch.cuda.set_device(local)
     os.environ.setdefault("TORCH_NCCL_HIGH_PRIORITY", "1"); dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     degree = int(sys.argv[1]) if len(sys.argv) > 1 else 2
-    mode = sys.argv[2] if len(sys.argv) > 2 else "euler"     # euler | viscous | weno | energy
+    mode = sys.argv[2] if len(sys.argv) > 2 else "euler"     # euler | peer | viscous | weno | energy
     px, py, pz = meshmod.factor3(world)
     m = meshmod.box(4 * px, 4 * py, 3 * pz, warp=0.1, seed=3)
     parts = meshmod.block_partition(m, px, py, pz)
@@ -143,7 +143,23 @@ def main():
     sp.SetSolutionColumn(part.gather_from_global(u, kf))
     n_steps, t = (3 if mode == "weno" else 5), 0.0
     dts = []
-    for _ in range(n_steps):
+    if mode == "peer":
+        # the same steps with the halo and the time-step minimum through peer-mapped memory (CUDA IPC), the whole
+        # step enqueued by the library; the time steps never reach the host, rank 0 replays them with the checker
+        from minicfd_b200 import peer
+        peer.connect(sp, part)
+        o_dt = oc.Oracle(m, degree, 0, 1)
+        for tag in range(6):
+            o_dt.set_bc(tag, 0)
+        ref_dt = u.copy()
+        for _ in range(n_steps):
+            sp.ctx.peer_step(3, t, 2e-3)
+            dt = o_dt.time_step(ref_dt, 2e-3, 3)
+            ref_dt = o_dt.rk_update(ref_dt, 3, t, dt)
+            dts.append(dt)
+            t += dt
+        sp.ctx.peer_check()
+    for _ in range(0 if mode == "peer" else n_steps):
         dt = sp.GetTimeStep(2e-3, 3)        # includes the all-reduce(MIN)
         RungeKutta(3).Update(sp, t, dt)
         dts.append(dt)
@@ -159,7 +175,9 @@ def main():
     dist.all_reduce(res)
     ok = True
     frame_ok = True
-    if mode == "euler":
+    if mode == "peer":
+        pass
+    elif mode == "euler":
         # frame output on N parts: rank 0 writes the .pvtu naming one piece per rank, every rank its own .vtu
         # (mini::mesh::vtk::Writer<Part>::WriteSolutions, vtk.hpp:541-573, 574-667)
         import tempfile

@@ -271,7 +271,7 @@ def test_multi_gpu_nccl_halo_matches_single_part():
     if n < 2:
         pytest.skip("needs at least 2 GPUs")
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    for degree, mode in ((2, "euler"), (3, "euler"), (2, "viscous"), (2, "weno"), (2, "energy")):
+    for degree, mode in ((2, "euler"), (2, "peer"), (3, "peer"), (3, "euler"), (2, "viscous"), (2, "weno"), (2, "energy")):
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
                "--master-addr", "127.0.0.1", "--master-port", "29533",
                os.path.join(root, "tests", "mgpu_worker.py"), str(degree), mode]
