@@ -8,7 +8,8 @@ loop (demo/euler/sourceless.cpp:187-215).  value = 3 * n_dof_total * steps / tim
 Workload (config 2 of BASELINE.json): synthetic structured box of 42^3 Hexahedron8 cells per GPU
 (10 001 880 DOF at p=2, K=5), FR-Lobatto p=2, HLLC, isentropic-vortex initial state, periodic
 wrap (the GPU-only performance variant), RK3.  N > 1: weak scaling, one 42^3
-block per GPU in a px*py*pz block partition, ghost-cell exchange over NCCL.
+block per GPU in a px*py*pz block partition; the ghost rows travel by stores into the neighbours' memory over
+NVLink (mcfd_peer_*; `--halo nccl`: the pack -> NCCL send/recv -> unpack path).
 
 Arms:
   (default)          our CUDA path.  `value`: state resident in HBM.  `e2e`: the same step through the
@@ -62,6 +63,9 @@ def parse():
                          "cell's VTK hexahedron, copied to the host), next to the reference's vtk::Writer::Prepare on the CPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--halo", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: ghost exchange by stores into the neighbours' memory (mcfd_peer_*, the default for the "
+                         "inviscid nodal schemes) or pack -> NCCL send/recv -> unpack issued from Python")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of replaying a CUDA graph")
     return ap.parse_args()
 
@@ -206,6 +210,11 @@ def cpu_run(args, steps, warmup, cells=None):
             "host_cores": cores, "ms_per_step": 1e3 * dt_wall / steps}
 
 
+def metric_name(args):
+    what = "Euler" if args.viscous is None else "Navier-Stokes"
+    return f"DOF-updates/s per RK stage (p={args.degree} {what}, hexa)"
+
+
 def config_dict(args, n_gpus, dims, part):
     return {"workload": f"BASELINE config 2: synthetic structured box, {dims[0]}x{dims[1]}x{dims[2]} Hexahedron8 "
                         f"cells total ({args.cells}^3 per GPU), "
@@ -230,11 +239,15 @@ def reference_arm(args):
     res = cpu_run(args, steps_run, warm_run)
     px, py, pz = __import__("minicfd_b200.mesh", fromlist=["factor3"]).factor3(args.gpus)
     dims = (args.cells * px, args.cells * py, args.cells * pz)
-    line = {"impl": "reference", "metric": "DOF-updates/s per RK stage (p=2 Euler, hexa)",
+    ours_cfg = config_dict(args, args.gpus, dims, f"{px}x{py}x{pz}")
+    ran = {"workload": "reference CPU code on a bounded sample of the workload: " + res["sample"],
+           "sample_of": ours_cfg["workload"], "step": ours_cfg["step"],
+           "parallelism": f"{res['cores']} host thread(s), one part each, in-process halo"}
+    line = {"impl": "reference", "metric": metric_name(args),
             "value": res["value"], "unit": "DOF-updates/s", "n_gpus": args.gpus, "steps": steps_run,
             "warmup": warm_run, "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": config_dict(args, args.gpus, dims, f"{px}x{py}x{pz}"),
+            "config": ran,
             "cpu_baseline": {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": res["value"], "unit": "DOF-updates/s", "h2d_bytes_per_step": 0,
                     "d2h_bytes_per_step": 0},
@@ -283,8 +296,14 @@ def ours(args):
         sp.SetLimiter(0.001, 1e-6)
     sp.ctx.set_stream(torch.cuda.current_stream().cuda_stream)
     sp.Approximate(lambda x: fields.vortex()(x, 0.0))
+    use_peer = (world > 1 and args.halo == "peer" and args.scheme != "dgm" and args.viscous is None
+                and not args.limiter and not args.energy_viscosity)
     if comm is not None:
         comm.exchange()
+    if use_peer:
+        from minicfd_b200 import peer
+        peer.connect(sp, part)
+    sums0 = conserved_sums(sp, part, args, world)
     rk = RungeKutta(3)
     n_dof_local = part.n_local * sp.kfields
     n_dof_total = n_dof_local * world
@@ -299,6 +318,9 @@ def ours(args):
 
     def step_device(t):
         # GetTimeStep (+ MIN over ranks) and Update without a host round trip: dt stays on the device
+        if use_peer:     # the whole step, halo and MIN included, enqueued by the library
+            sp.ctx.peer_step(3, t, 1.0)
+            return 0.0
         time_step_device(sp, 1.0, 3, dt_dev)
         rk.UpdateDevice(sp, t, dt_dev.data_ptr())
         return 0.0
@@ -306,11 +328,14 @@ def ours(args):
     t = 0.0
     for _ in range(max(args.warmup, 3)):
         t += step_device(t)
-    # One step (GetTimeStep + 3 stages incl. the halo exchange) captured once as a CUDA graph and
-    # replayed: the host launches one graph per step instead of ~10 kernels and 6 NCCL operations.
+    # THREE steps (each GetTimeStep [+ MIN over ranks] + 3 stages [+ ghost exchange]) captured once as a CUDA graph and
+    # replayed: the three state buffers rotate with period three, so the replays march on in time exactly like host
+    # launches do.  At N > 1 the peer path is captured the same way (its push counts live on the device); the NCCL
+    # path is launched from the host (replay with NCCL point-to-point inside was slower and did not shut down cleanly).
+    kGraphSteps = 3
     graph = None
-    launches_per_step = None
-    if not args.no_graph and world == 1:   # with NCCL point-to-point inside, replay was slower and did not shut down cleanly
+    launches_per_graph = None
+    if not args.no_graph and (world == 1 or use_peer):
         try:
             barrier()
             l0 = sp.ctx.launch_count()
@@ -319,13 +344,16 @@ def ours(args):
             cap_stream.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(cap_stream):
                 sp.ctx.set_stream(cap_stream.cuda_stream)
-                with torch.cuda.graph(graph, stream=cap_stream):
-                    step_device(t)
+                with torch.cuda.graph(graph, stream=cap_stream, capture_error_mode="relaxed"):
+                    for _ in range(kGraphSteps):
+                        step_device(t)
+                    if use_peer:
+                        sp.ctx.peer_join()      # the library's side stream rejoins the captured one
                 sp.ctx.set_stream(torch.cuda.current_stream().cuda_stream)
-            launches_per_step = sp.ctx.launch_count() - l0
+            launches_per_graph = sp.ctx.launch_count() - l0
             torch.cuda.current_stream().wait_stream(cap_stream)
             sp.ctx.set_stream(torch.cuda.current_stream().cuda_stream)
-            for _ in range(3):
+            for _ in range(2):
                 graph.replay()
             barrier()
         except Exception as e:  # capture not possible: fall back to host launches, and say so
@@ -334,12 +362,21 @@ def ours(args):
                       file=sys.stderr)
             graph = None
             sp.ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+    if world > 1:    # all ranks replay, or none does
+        ok = torch.tensor([1.0 if (graph is not None or not use_peer or args.no_graph) else 0.0], device="cuda")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if ok.item() == 0.0:
+            raise SystemExit("bench.py: graph capture succeeded on some ranks only")
 
-    def run_step(tt):
+    def run_steps(tt, n_steps):
+        done = 0
         if graph is not None:
-            graph.replay()
-            return 0.0
-        return step_device(tt)
+            for _ in range(n_steps // kGraphSteps):
+                graph.replay()
+            done = n_steps // kGraphSteps * kGraphSteps
+        for _ in range(n_steps - done):
+            tt += step_device(tt)
+        return tt
 
     launches0 = sp.ctx.launch_count()
     barrier()
@@ -349,14 +386,15 @@ def ours(args):
         clocks.mark_begin()
         e0.record()
         host_t0 = time.perf_counter()
-        for _ in range(args.steps):
-            t += run_step(t)
+        t = run_steps(t, args.steps)
         host_issue_ms = 1e3 * (time.perf_counter() - host_t0)   # time the host needed to issue the steps
         e1.record()
         barrier()
         clocks.mark_end()
     ms = e0.elapsed_time(e1)
-    launches = (sp.ctx.launch_count() - launches0) if graph is None else launches_per_step * args.steps
+    launches = sp.ctx.launch_count() - launches0
+    if graph is not None:
+        launches += launches_per_graph * (args.steps // kGraphSteps)
     # duration of the stage kernel: CUDA events around every stage launch, on the launching stream, over
     # the same steps launched from the host right after the timed region (events cannot sit in a graph)
     k_steps = min(args.steps, 20)
@@ -366,6 +404,9 @@ def ours(args):
     barrier()
     kernel_ms, kernel_launches = sp.ctx.kernel_time(reset=True)
     sp.ctx.enable_kernel_timing(False)
+    if use_peer:
+        sp.ctx.peer_check()
+    sums1 = conserved_sums(sp, part, args, world)
     tmax = torch.tensor([ms], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
@@ -383,6 +424,12 @@ def ours(args):
             # the user's loop on host columns: SetSolutionColumn(host) -> GetTimeStep -> Update ->
             # GetSolutionColumn(host); the output buffer of one step is the input of the next
             sp.ctx.set_solution(bufs[0].numpy())          # H2D from pinned memory (ghosts: refreshed in Update)
+            if use_peer:
+                sp.ctx.peer_push()                        # the new solution's ghost images
+                sp.ctx.peer_step(3, tt, 1.0)
+                sp.ctx.get_solution(bufs[1].numpy())
+                bufs.reverse()
+                return 0.0
             dt = sp.GetTimeStep(1.0, 3)                   # includes the D2H read of dt
             rk.Update(sp, tt, dt)
             sp.ctx.get_solution(bufs[1].numpy())          # D2H of the step's result
@@ -424,12 +471,17 @@ def ours(args):
         traffic_path = os.path.join(ROOT, "profiles", "stage_kernel_traffic.json")
         if os.path.exists(traffic_path):
             roofline["traffic"] = json.load(open(traffic_path)).get("dram_bytes_per_launch")
-        line = {"metric": "DOF-updates/s per RK stage (p=2 Euler, hexa)", "value": value, "unit": "DOF-updates/s",
+        line = {"metric": metric_name(args), "value": value, "unit": "DOF-updates/s",
                 "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": dict(config_dict(args, world, dims, f"{px}x{py}x{pz}"), cuda_graph=graph is not None),
+                "config": dict(config_dict(args, world, dims, f"{px}x{py}x{pz}"),
+                               cuda_graph=(f"{kGraphSteps} steps per replay" if graph is not None else False)),
                 "clocks": clocks.summary(),
                 "roofline": roofline, "gpu_launches": int(launches),
+                "halo": ("none (one part)" if world == 1 else
+                         "peer stores + epoch words, step enqueued by the library (mcfd_peer_step)" if use_peer else
+                         "pack -> NCCL send/recv -> unpack, issued per stage from Python"),
+                "check": conservation_check(sums0, sums1),
                 "host_issue_ms_per_step": host_issue_ms / args.steps}
         if e2e is not None:
             line["e2e"] = e2e
@@ -442,7 +494,38 @@ def ours(args):
     if world > 1:
         comm.drain()
         torch.cuda.synchronize()
+        dist.barrier()
         dist.destroy_process_group()
+
+
+def conserved_sums(sp, part, args, world):
+    """Integrals of the five conserved variables over the whole (periodic) domain: sum over ranks of
+    sum_cells sum_nodes w_i w_j w_k det(J) u — a correctness signal that costs one column read.  With a periodic
+    wrap the scheme conserves them to rounding, and only if every face sees the same two states on both sides, i.e.
+    only if the ghost rows are the neighbours' current values."""
+    import torch
+    import torch.distributed as dist
+    if args.scheme == "dgm":
+        return None
+    q = args.degree + 1
+    w1 = {3: np.array([1.0, 4.0, 1.0]) / 3, 4: np.array([1.0, 5.0, 5.0, 1.0]) / 6}[q]
+    w = (w1[:, None, None] * w1[None, :, None] * w1[None, None, :]).reshape(-1)
+    det = sp.ctx.jacobian_determinants()                      # [n_local][N]
+    u = sp.GetSolutionColumn().reshape(part.n_local, q ** 3, 5)
+    sums = torch.from_numpy(np.einsum("cn,n,cnk->k", det, w, u)).cuda()
+    if world > 1:
+        dist.all_reduce(sums)
+    return sums.cpu().numpy()
+
+
+def conservation_check(s0, s1):
+    if s0 is None or s1 is None:
+        return None
+    scale = np.maximum(np.abs(s0), np.abs(s0).max() * 1e-3)
+    drift = float(np.max(np.abs(s1 - s0) / scale))
+    return {"what": "relative drift of the global integrals of (rho, rho u, rho v, rho w, E) over the timed run "
+                    "(periodic domain: conserved to rounding only if every ghost row is current)",
+            "conservation_rel_drift": drift, "finite": bool(np.isfinite(s1).all()), "ok": bool(drift < 1e-10)}
 
 
 def frame_output(sp, args):

@@ -147,45 +147,51 @@ int mcfd_halo_pack(mcfd_ctx *ctx);
  * the ghost cells of the current solution. */
 int mcfd_halo_unpack(mcfd_ctx *ctx);
 
-/* -- the same exchange through peer-mapped memory --------------------------------------------------------------
+/* -- the same exchange between parts on the GPUs of one node ------------------------------------------------------
  * Part::ShareGhostCellCoeffs / UpdateGhostCellCoeffs (part.hpp:1242-1314) and the MPI_Allreduce(MIN) of the time step
- * (demo/euler/sourceless.cpp:194) for parts placed one per GPU of an NVLink / NVSwitch node: the send cells' rows are
- * stored straight into the rows of their ghost images in the neighbours' state buffers and an epoch word per
- * neighbour tells when they have arrived (minicfd_b200/csrc/peer.cuh) — no packing, no message library, no host in
- * the loop.  Set-up, after mcfd_set_mesh and mcfd_set_halo on every rank:
- *   1. mcfd_peer_export: allocates the epoch words and time-step slots and returns, for the three state buffers, the
- *      epoch words and the slots (in this order), plain device pointers (for contexts driven by one process, after
- *      cudaDeviceEnablePeerAccess) and / or CUDA IPC handles (one process per GPU; send them to the other ranks);
+ * (demo/euler/sourceless.cpp:194) for parts placed one per GPU of an NVLink / NVSwitch node, without a message library
+ * and without the host in the loop (minicfd_b200/csrc/peer.cuh): the send cells' rows are packed into a send stage —
+ * by the stage kernel itself where it can —, the copy engines take them to the neighbours' receive stages through the
+ * peer mapping, an epoch word per neighbour tells when they have arrived, and the receiving stage kernel polls that
+ * word itself.  Set-up, after mcfd_set_mesh and mcfd_set_halo on every rank:
+ *   1. mcfd_peer_export allocates the stages, words and time-step slots and returns three buffers — the epoch words,
+ *      the time-step slots, the receive stage, in this order — as plain device pointers (contexts driven by one
+ *      process; different GPUs need cudaDeviceEnablePeerAccess) and / or CUDA IPC handles (one process per GPU);
  *   2. mcfd_peer_open turns a handle received from another process into a pointer valid on this context's device;
- *   3. mcfd_peer_connect: neighbour_state[3 i + b] = state buffer b of the i-th neighbour (the order of mcfd_set_halo),
- *      neighbour_flags[i] = its epoch words, slot_at_neighbour[i] = this part's index in THAT part's neighbour list,
- *      dest_cells = for every send cell (all neighbours back to back, the order of mcfd_set_halo) the id of its ghost
- *      image in the neighbour's numbering (= the neighbour's recv list for this part); world_flags[r], world_dt_slots[r]
- *      = the epoch words and slots of every rank r, this one included.
- * mcfd_peer_push sends the send cells of the state the next residual reads (the current solution, or the stage input
- * inside an open RK step); mcfd_peer_wait holds the stream until every neighbour's push of the same count has arrived.
- * Every rank must push the same number of times.  mcfd_peer_min_time_step replaces the value in dt_dev (NULL: the
- * context's own, mcfd_time_step_device) by the minimum over all ranks.  mcfd_peer_step is one whole
- * GetTimeStep + MPI_Allreduce(MIN) + RungeKutta<order>::Update (sourceless.cpp:191-196, rk.hpp:16-56) with the inner
- * cells on the context's stream and the inter cells, waits and pushes on a high-priority stream of its own; it leaves
- * the ghost rows of the new solution on their way.  Nothing synchronises with the host; mcfd_peer_check does, and
- * reports a wait that gave up (about ten seconds of polling).  While a step is enqueued do not call anything that
- * synchronises the device implicitly (cudaMalloc, cudaFree, the blocking getters of this library) on a rank whose
- * neighbours have not enqueued theirs: the kernels that poll would wait for work that never gets enqueued. */
+ *   3. mcfd_peer_connect, per neighbour i (the order of mcfd_set_halo): neighbour_flags[i] = its epoch words,
+ *      slot_at_neighbour[i] = this part's index in THAT part's neighbour list, neighbour_recv[i] = its receive stage,
+ *      neighbour_recv_items[i] = the number of cells in its recv lists (all its neighbours), offset_at_neighbour[i] =
+ *      where this part's cells start among them; world_flags[r], world_dt_slots[r] = the epoch words and time-step
+ *      slots of every rank r, this one included.  The two parts' lists must name the same cells in the same order.
+ * mcfd_peer_push delivers the send cells of the state the next residual reads (the current solution, or the stage input
+ * inside an open RK step); mcfd_peer_wait holds the stream until every neighbour's delivery of the same count has
+ * arrived and unpacks it into the ghost rows.  Every rank must push equally often, and again after every
+ * mcfd_set_solution*.  mcfd_peer_min_time_step replaces the value in dt_dev (NULL: the context's own,
+ * mcfd_time_step_device) by the minimum over all ranks.  mcfd_peer_step is one whole GetTimeStep + MPI_Allreduce(MIN) +
+ * RungeKutta<order>::Update (sourceless.cpp:191-196, rk.hpp:16-56) for the inviscid nodal schemes; the deliveries of
+ * the stage results run on a stream of the context's own beside the next stage.  All counts live on the device, so
+ * captured steps can be replayed as a CUDA graph: capture three steps (the buffers rotate with period three) after at
+ * least one step has run, end the capture with mcfd_peer_join (the side stream rejoins the context's), and have every
+ * rank replay equally often.  Nothing synchronises with the host; mcfd_peer_check does, and reports a wait that gave
+ * up (about ten seconds of polling).  While a step is enqueued do not call anything that synchronises the device
+ * implicitly (cudaMalloc, cudaFree, the blocking getters of this library) on a rank whose neighbours have not
+ * enqueued theirs: the kernels that poll would wait for work that never gets enqueued. */
 typedef struct { unsigned char bytes[64]; } mcfd_ipc_handle;   /* cudaIpcMemHandle_t */
-int mcfd_peer_export(mcfd_ctx *ctx, int32_t world, mcfd_ipc_handle *handles /* [5] or NULL */, void **pointers /* [5] or NULL */);
+int mcfd_peer_export(mcfd_ctx *ctx, int32_t world, mcfd_ipc_handle *handles /* [3] or NULL */, void **pointers /* [3] or NULL */);
 int mcfd_peer_open(mcfd_ctx *ctx, const mcfd_ipc_handle *handle, void **pointer);
-int mcfd_peer_connect(mcfd_ctx *ctx, int32_t rank, int32_t world, int32_t n_neighbours, void *const *neighbour_state,
-                      void *const *neighbour_flags, const int32_t *slot_at_neighbour, const int64_t *dest_cells,
-                      void *const *world_flags, void *const *world_dt_slots);
+int mcfd_peer_connect(mcfd_ctx *ctx, int32_t rank, int32_t world, int32_t n_neighbours, void *const *neighbour_flags,
+                      const int32_t *slot_at_neighbour, void *const *neighbour_recv, const int64_t *neighbour_recv_items,
+                      const int64_t *offset_at_neighbour, void *const *world_flags, void *const *world_dt_slots);
 int mcfd_peer_push(mcfd_ctx *ctx);
 int mcfd_peer_wait(mcfd_ctx *ctx);
 int mcfd_peer_min_time_step(mcfd_ctx *ctx, double *dt_dev);
 int mcfd_peer_step(mcfd_ctx *ctx, int order, double t, double dt_guess);
 /* The same for several contexts driven by one host thread (one per GPU, or several on one GPU): they advance in
- * lockstep, every push enqueued before any wait that depends on it.  With contexts of ONE process use this call, not
- * mcfd_peer_step on each in turn: a context's step polls for pushes that the next context's call has yet to enqueue. */
+ * lockstep, every delivery enqueued before any wait that depends on it.  With contexts of ONE process use this call,
+ * not mcfd_peer_step on each in turn: a context's step polls for deliveries that the next context's call has yet to
+ * enqueue. */
 int mcfd_peer_step_group(mcfd_ctx *const *ctxs, int32_t n, int order, double t, double dt_guess);
+int mcfd_peer_join(mcfd_ctx *ctx);
 int mcfd_peer_check(mcfd_ctx *ctx);
 
 /* -- boundary conditions (fem.hpp:71-74, 196-222) -------------------------------------------- */

@@ -101,13 +101,14 @@ SYMBOLS = {
     "mcfd_riemann_flux": (C.c_int, [_P, C.c_int32, C.c_int64, _D, _D, _D, _D]),
     "mcfd_peer_export": (C.c_int, [_P, C.c_int32, _P, C.POINTER(_P)]),
     "mcfd_peer_open": (C.c_int, [_P, _P, C.POINTER(_P)]),
-    "mcfd_peer_connect": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, C.POINTER(_P), C.POINTER(_P), _I32, _I64,
+    "mcfd_peer_connect": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, C.POINTER(_P), _I32, C.POINTER(_P), _I64, _I64,
                                     C.POINTER(_P), C.POINTER(_P)]),
     "mcfd_peer_push": (C.c_int, [_P]),
     "mcfd_peer_wait": (C.c_int, [_P]),
     "mcfd_peer_min_time_step": (C.c_int, [_P, _P]),
     "mcfd_peer_step": (C.c_int, [_P, C.c_int, C.c_double, C.c_double]),
     "mcfd_peer_step_group": (C.c_int, [C.POINTER(_P), C.c_int32, C.c_int, C.c_double, C.c_double]),
+    "mcfd_peer_join": (C.c_int, [_P]),
     "mcfd_peer_check": (C.c_int, [_P]),
 }
 
@@ -332,12 +333,12 @@ class Context:
 
     # ---- halo through peer-mapped memory (mcfd_peer_*) ----
     def peer_export(self, world):
-        """-> (five 64-byte IPC handles, five device pointers): state buffers 0..2, epoch words, dt slots."""
-        handles = (C.c_ubyte * (5 * 64))()
-        ptrs = (_P * 5)()
+        """-> (three 64-byte IPC handles, three device pointers): epoch words, time-step slots, receive stage."""
+        handles = (C.c_ubyte * (3 * 64))()
+        ptrs = (_P * 3)()
         self._check(self.lib.mcfd_peer_export(self.h, world, C.cast(handles, _P), ptrs))
         raw = bytes(handles)
-        return [raw[64 * i:64 * (i + 1)] for i in range(5)], [p or 0 for p in ptrs]
+        return [raw[64 * i:64 * (i + 1)] for i in range(3)], [p or 0 for p in ptrs]
 
     def peer_open(self, handle: bytes) -> int:
         buf = (C.c_ubyte * 64).from_buffer_copy(handle)
@@ -345,16 +346,21 @@ class Context:
         self._check(self.lib.mcfd_peer_open(self.h, C.cast(buf, _P), C.byref(out)))
         return out.value
 
-    def peer_connect(self, rank, world, neighbour_state, neighbour_flags, slot_at_neighbour, dest_cells, world_flags,
-                     world_dt_slots):
+    def peer_connect(self, rank, world, neighbour_flags, slot_at_neighbour, neighbour_recv, neighbour_recv_items,
+                     offset_at_neighbour, world_flags, world_dt_slots):
         n = len(neighbour_flags)
-        st = (_P * max(1, 3 * n))(*[p for trio in neighbour_state for p in trio])
         fl = (_P * max(1, n))(*neighbour_flags)
+        rv = (_P * max(1, n))(*neighbour_recv)
         slots = np.ascontiguousarray(slot_at_neighbour, dtype=np.int32)
-        dest = np.ascontiguousarray(dest_cells, dtype=np.int64)
+        items = np.ascontiguousarray(neighbour_recv_items, dtype=np.int64)
+        offs = np.ascontiguousarray(offset_at_neighbour, dtype=np.int64)
         wf = (_P * world)(*world_flags)
         ws = (_P * world)(*world_dt_slots)
-        self._check(self.lib.mcfd_peer_connect(self.h, rank, world, n, st, fl, slots.ctypes.data_as(_I32), _ip(dest), wf, ws))
+        self._check(self.lib.mcfd_peer_connect(self.h, rank, world, n, fl, slots.ctypes.data_as(_I32), rv, _ip(items),
+                                               _ip(offs), wf, ws))
+
+    def peer_join(self):
+        self._check(self.lib.mcfd_peer_join(self.h))
 
     def peer_push(self):
         self._check(self.lib.mcfd_peer_push(self.h))

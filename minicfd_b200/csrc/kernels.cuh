@@ -124,6 +124,22 @@ struct StageArgs {
   const double *cell_nu;        // [tile][comp][lane] kDiffIsotropic: viscosity of every component, per cell
   Viscosity vis;
   const unsigned char *line_bytes;   // LineStageKernel only: LineTableBytes() in device memory
+  // LineStageKernel as ONE launch per stage on a part with neighbours (peer.cuh; all null / 0 otherwise).
+  // Receiving: the blocks with inter cells, which come last (part.hpp:746-767 numbers those cells last), first wait until
+  // this part's epoch words carry the count of the delivery of the stage input, and read the ghost states from the
+  // receive stage [row][ghost item] instead of ghost rows.  Sending: they store a second copy of their send cells'
+  // new values into the send stage [row][send item], which the copy engines take to the neighbours after the launch.
+  struct PeerStage {
+    int on, first_block, first_cell, n_neighbours, wait_add, n_send, n_recv;
+    const unsigned long long *flags;    // my epoch words
+    const unsigned long long *counts;   // peer.cuh: kPeerPlain, kPeerStageBase; expected = plain + stage_base + wait_add
+    const double *recv;                 // receive stage of the stage INPUT
+    const int *recv_index;              // [n_ghost] ghost cell n_local + i -> its item
+    double *send;                       // send stage of the stage OUTPUT
+    const int *tgt_offset;              // [n_local - first_cell + 1] send items of local cell first_cell + i ...
+    const int *tgt_item;                // ... listed here
+    int *error;
+  } peer;
 };
 
 // diffusive part of the Riemann type, a template parameter of the stage kernel
@@ -2220,6 +2236,7 @@ __global__ void RiemannKernel(int bc_kind, int n, const double *normals, const d
 
 }  // namespace mcfd
 
+#include "peer.cuh"
 #include "stage_lines.cuh"
 
 #endif  // MINICFD_B200_KERNELS_CUH_

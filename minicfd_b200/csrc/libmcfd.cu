@@ -11,7 +11,6 @@
 
 #include "../../include/minicfd_b200.h"
 #include "kernels.cuh"
-#include "peer.cuh"
 #include "format.cuh"
 #include "shuffle.cuh"
 #include "tables.hpp"
@@ -101,22 +100,26 @@ struct mcfd_ctx {
   int64_t inner_blocks = 0, total_blocks = 0;  // CTA-sized blocks without / with ghost neighbours
   // ---- halo through peer-mapped memory (mcfd_peer_*): the send cells' rows go straight into the neighbours' ghost rows
   struct Peer {
-    bool connected = false;
+    bool connected = false, pushed_once = false;
     int n_neighbours = 0, rank = 0, world = 1;
-    DevBuf<unsigned long long> flags;            // [kPeerWords]: halo epochs per neighbour slot, then dt epochs per rank
+    DevBuf<unsigned long long> flags;            // [kPeerWords]: delivery counts per neighbour slot, then dt epochs per rank
+    DevBuf<unsigned long long> counts;           // [kPeerCounts] peer.cuh: what the device keeps count of
     DevBuf<double> dt_slots;                     // [2][world]: every rank's time step, by step parity
-    DevBuf<int> dest_cells;                      // ghost cell id at the neighbour, per send item
-    DevBuf<int> item_neighbour;                  // neighbour slot, per send item
-    DevBuf<double *> state_dev;                  // [n_neighbours][3] the neighbours' state buffers
-    DevBuf<unsigned long long *> flag_dev;       // [n_neighbours] the word to signal at each neighbour
+    DevBuf<double> send_stage, recv_stage;       // [3][fields][n_send | n_recv]: packed halo per state buffer
+    DevBuf<int> recv_index;                      // [n_ghost] ghost cell -> item of the receive stage
+    DevBuf<int> tgt_offset, tgt_item;            // per local cell from first_inter on: its items of the send stage
+    std::vector<double *> nbr_recv;              // [n_neighbours] the neighbour's receive stage, at this part's segment
+    std::vector<int64_t> nbr_recv_total;         // [n_neighbours] row length of that stage
+    std::vector<int64_t> send_offset;            // [n_neighbours + 1] this part's segments of the send stage
+    DevBuf<unsigned long long *> flag_dev;       // [n_neighbours] the word to raise at each neighbour
     DevBuf<double *> dt_slot_dev;                // [world] every rank's dt_slots
     DevBuf<unsigned long long *> dt_flag_dev;    // [world] every rank's dt epoch word for this rank
-    DevBuf<unsigned int> done;                   // block counter of the push kernel
     DevBuf<int> error;                           // set when a wait gave up
     std::vector<void *> opened;                  // cudaIpcOpenMemHandle results
-    unsigned long long halo_epoch = 0, dt_epoch = 0;
+    int deliveries_this_step = 0;                // stage deliveries of the step in progress / just finished (host side)
     cudaStream_t side = nullptr;
-    cudaEvent_t ev_main = nullptr, ev_side = nullptr;
+    cudaEvent_t ev_main = nullptr, ev_side = nullptr, ev_copy[3] = {nullptr, nullptr, nullptr};
+    unsigned long long ev_copy_capture[3] = {~0ull, ~0ull, ~0ull};   // capture the event was recorded in (0: none; ~0: never)
   } peer;
 };
 
@@ -297,9 +300,10 @@ cudaError_t LaunchDgmQ(mcfd_ctx *ctx, DgmArgs const &a, int t0, int n_tiles) {
 
 // Launch the stage kernel over CTA blocks [block_begin, block_end).
 int LaunchStage(mcfd_ctx *ctx, const double *u_in, const double *u0, double *u_out, int mode,
-    double dt, int64_t block_begin, int64_t block_end) {
+    double dt, int64_t block_begin, int64_t block_end, const StageArgs::PeerStage *fused = nullptr) {
   if (block_end <= block_begin) return MCFD_OK;
-  StageArgs a;
+  StageArgs a{};
+  if (fused) a.peer = *fused;
   a.u_in = u_in; a.u0 = u0; a.u_out = u_out;
   a.geom = ctx->geom.p; a.nbr = ctx->nbr.p; a.code = ctx->code.p;
   a.bkind = ctx->bkind.p; a.bvals = ctx->bvals.p;
@@ -508,6 +512,7 @@ int mcfd_destroy(mcfd_ctx *ctx) {
   for (void *p : ctx->peer.opened) cudaIpcCloseMemHandle(p);
   if (ctx->peer.ev_main) cudaEventDestroy(ctx->peer.ev_main);
   if (ctx->peer.ev_side) cudaEventDestroy(ctx->peer.ev_side);
+  for (auto e : ctx->peer.ev_copy) if (e) cudaEventDestroy(e);
   if (ctx->peer.side) cudaStreamDestroy(ctx->peer.side);
   delete ctx;
   return MCFD_OK;
@@ -1130,21 +1135,28 @@ int mcfd_rk_step_device(mcfd_ctx *ctx, int order, double t, const double *dt_dev
   return MCFD_OK;
 }
 
-// ---- halo and time-step minimum through peer-mapped memory (peer.cuh) -------------------------------------------
+// ---- halo and time-step minimum between parts on the GPUs of one node (peer.cuh) ----------------------------------
 
 int mcfd_peer_export(mcfd_ctx *ctx, int32_t world, mcfd_ipc_handle *handles, void **pointers) {
   if (int s = RequireMesh(ctx)) return s;
   if (world < 1 || world > kPeerMaxRanks) return Fail(ctx, MCFD_ERR_ARG, "world size must be 1..64");
   auto &pe = ctx->peer;
   pe.world = world;
+  const size_t n_recv = ctx->recv_cells.n, n_send = ctx->send_cells.n;
   MCFD_CUDA(ctx, pe.flags.Alloc(kPeerWords));
   MCFD_CUDA(ctx, cudaMemset(pe.flags.p, 0, kPeerWords * sizeof(unsigned long long)));
+  MCFD_CUDA(ctx, pe.counts.Alloc(kPeerCounts));
+  MCFD_CUDA(ctx, cudaMemset(pe.counts.p, 0, kPeerCounts * sizeof(unsigned long long)));
   MCFD_CUDA(ctx, pe.dt_slots.Alloc(2 * (size_t)world));
   MCFD_CUDA(ctx, cudaMemset(pe.dt_slots.p, 0, 2 * (size_t)world * sizeof(double)));
-  pe.halo_epoch = pe.dt_epoch = 0;
+  MCFD_CUDA(ctx, pe.recv_stage.Alloc(std::max<size_t>(1, 3 * n_recv * ctx->fields)));
+  MCFD_CUDA(ctx, pe.send_stage.Alloc(std::max<size_t>(1, 3 * n_send * ctx->fields)));
+  MCFD_CUDA(ctx, cudaMemset(pe.recv_stage.p, 0, pe.recv_stage.n * sizeof(double)));
+  pe.pushed_once = false;
   pe.connected = false;
-  void *ptrs[5] = {ctx->u[0].p, ctx->u[1].p, ctx->u[2].p, pe.flags.p, pe.dt_slots.p};
-  for (int i = 0; i < 5; ++i) {
+  pe.deliveries_this_step = 0;
+  void *ptrs[3] = {pe.flags.p, pe.dt_slots.p, pe.recv_stage.p};
+  for (int i = 0; i < 3; ++i) {
     if (pointers) pointers[i] = ptrs[i];
     if (handles) {
       static_assert(sizeof(cudaIpcMemHandle_t) == sizeof(mcfd_ipc_handle), "handle size");
@@ -1167,32 +1179,53 @@ int mcfd_peer_open(mcfd_ctx *ctx, const mcfd_ipc_handle *handle, void **pointer)
   return MCFD_OK;
 }
 
-int mcfd_peer_connect(mcfd_ctx *ctx, int32_t rank, int32_t world, int32_t n_neighbours, void *const *neighbour_state,
-    void *const *neighbour_flags, const int32_t *slot_at_neighbour, const int64_t *dest_cells, void *const *world_flags,
-    void *const *world_dt_slots) {
+int mcfd_peer_connect(mcfd_ctx *ctx, int32_t rank, int32_t world, int32_t n_neighbours, void *const *neighbour_flags,
+    const int32_t *slot_at_neighbour, void *const *neighbour_recv, const int64_t *neighbour_recv_items,
+    const int64_t *offset_at_neighbour, void *const *world_flags, void *const *world_dt_slots) {
   if (int s = RequireMesh(ctx)) return s;
   auto &pe = ctx->peer;
   if (!pe.flags.p || world != pe.world) return Fail(ctx, MCFD_ERR_STATE, "call mcfd_peer_export with this world size first");
   if (rank < 0 || rank >= world || n_neighbours < 0 || n_neighbours > kPeerMaxNeighbours ||
       n_neighbours != (int)ctx->send_counts.size())
     return Fail(ctx, MCFD_ERR_ARG, "rank / neighbour count does not match mcfd_set_halo");
-  if (!world_flags || !world_dt_slots || (n_neighbours && (!neighbour_state || !neighbour_flags || !slot_at_neighbour || !dest_cells)))
+  if (!world_flags || !world_dt_slots || (n_neighbours && (!neighbour_flags || !slot_at_neighbour || !neighbour_recv ||
+                                                            !neighbour_recv_items || !offset_at_neighbour)))
     return Fail(ctx, MCFD_ERR_ARG, "null argument");
-  const size_t n_items = ctx->send_cells.n;
-  std::vector<int> dest(n_items), item_nbr(n_items);
-  size_t x = 0;
-  for (int i = 0; i < n_neighbours; ++i)
-    for (int64_t k = 0; k < ctx->send_counts[i]; ++k, ++x) {
-      if (dest_cells[x] < 0 || dest_cells[x] >= ((int64_t)1 << 30)) return Fail(ctx, MCFD_ERR_ARG, "bad destination cell");
-      dest[x] = (int)dest_cells[x];
-      item_nbr[x] = i;
-    }
-  std::vector<double *> st(3 * (size_t)n_neighbours);
-  std::vector<unsigned long long *> fl(n_neighbours);
+  const size_t n_send = ctx->send_cells.n, n_recv = ctx->recv_cells.n;
+  const int64_t first = ctx->first_inter, n_local = ctx->mesh.n_local;
+  // the halo lists seen from the cells: every local cell's items of the send stage, every ghost cell's item of the
+  // receive stage
+  std::vector<int> send_host(n_send), recv_host(n_recv);
+  if (n_send) MCFD_CUDA(ctx, cudaMemcpy(send_host.data(), ctx->send_cells.p, n_send * sizeof(int), cudaMemcpyDeviceToHost));
+  if (n_recv) MCFD_CUDA(ctx, cudaMemcpy(recv_host.data(), ctx->recv_cells.p, n_recv * sizeof(int), cudaMemcpyDeviceToHost));
+  std::vector<int> off(n_local - first + 2, 0);
+  for (size_t k = 0; k < n_send; ++k) {
+    if (send_host[k] < first) return Fail(ctx, MCFD_ERR_STATE, "a send cell precedes the first inter cell");
+    ++off[send_host[k] - first + 1];
+  }
+  for (size_t c = 1; c < off.size(); ++c) off[c] += off[c - 1];
+  std::vector<int> items(std::max<size_t>(n_send, 1)), fill(off.begin(), off.end() - 1);
+  for (size_t k = 0; k < n_send; ++k) items[fill[send_host[k] - first]++] = (int)k;
+  std::vector<int> ridx(std::max<int64_t>(ctx->mesh.n_ghost, 1), 0);
+  for (size_t k = 0; k < n_recv; ++k) ridx[recv_host[k] - n_local] = (int)k;
+  MCFD_CUDA(ctx, pe.tgt_offset.Alloc(off.size()));
+  MCFD_CUDA(ctx, pe.tgt_item.Alloc(items.size()));
+  MCFD_CUDA(ctx, pe.recv_index.Alloc(ridx.size()));
+  MCFD_CUDA(ctx, cudaMemcpy(pe.tgt_offset.p, off.data(), off.size() * sizeof(int), cudaMemcpyHostToDevice));
+  MCFD_CUDA(ctx, cudaMemcpy(pe.tgt_item.p, items.data(), items.size() * sizeof(int), cudaMemcpyHostToDevice));
+  MCFD_CUDA(ctx, cudaMemcpy(pe.recv_index.p, ridx.data(), ridx.size() * sizeof(int), cudaMemcpyHostToDevice));
+  pe.nbr_recv.assign(n_neighbours, nullptr);
+  pe.nbr_recv_total.assign(n_neighbours, 0);
+  pe.send_offset.assign(n_neighbours + 1, 0);
+  std::vector<unsigned long long *> fl(std::max(n_neighbours, 1), nullptr);
   for (int i = 0; i < n_neighbours; ++i) {
     if (slot_at_neighbour[i] < 0 || slot_at_neighbour[i] >= kPeerMaxNeighbours) return Fail(ctx, MCFD_ERR_ARG, "bad neighbour slot");
-    for (int b = 0; b < 3; ++b) st[3 * i + b] = static_cast<double *>(neighbour_state[3 * i + b]);
+    if (offset_at_neighbour[i] < 0 || offset_at_neighbour[i] + ctx->send_counts[i] > neighbour_recv_items[i])
+      return Fail(ctx, MCFD_ERR_ARG, "this part's segment does not fit the neighbour's receive stage");
     fl[i] = static_cast<unsigned long long *>(neighbour_flags[i]) + slot_at_neighbour[i];
+    pe.nbr_recv[i] = static_cast<double *>(neighbour_recv[i]) + offset_at_neighbour[i];
+    pe.nbr_recv_total[i] = neighbour_recv_items[i];
+    pe.send_offset[i + 1] = pe.send_offset[i] + ctx->send_counts[i];
   }
   std::vector<double *> ds(world);
   std::vector<unsigned long long *> df(world);
@@ -1200,38 +1233,40 @@ int mcfd_peer_connect(mcfd_ctx *ctx, int32_t rank, int32_t world, int32_t n_neig
     ds[r] = static_cast<double *>(world_dt_slots[r]);
     df[r] = static_cast<unsigned long long *>(world_flags[r]) + kPeerMaxNeighbours + rank;
   }
-  MCFD_CUDA(ctx, pe.dest_cells.Alloc(n_items));
-  MCFD_CUDA(ctx, pe.item_neighbour.Alloc(n_items));
-  MCFD_CUDA(ctx, pe.state_dev.Alloc(st.size()));
   MCFD_CUDA(ctx, pe.flag_dev.Alloc(fl.size()));
   MCFD_CUDA(ctx, pe.dt_slot_dev.Alloc(world));
   MCFD_CUDA(ctx, pe.dt_flag_dev.Alloc(world));
-  MCFD_CUDA(ctx, pe.done.Alloc(1));
   MCFD_CUDA(ctx, pe.error.Alloc(1));
-  if (!ctx->dt_dev.p) MCFD_CUDA(ctx, ctx->dt_dev.Alloc(1));   // not inside a step: cudaMalloc may wait for kernels that poll
-  MCFD_CUDA(ctx, cudaMemset(pe.done.p, 0, sizeof(unsigned int)));
   MCFD_CUDA(ctx, cudaMemset(pe.error.p, 0, sizeof(int)));
-  if (n_items) {
-    MCFD_CUDA(ctx, cudaMemcpy(pe.dest_cells.p, dest.data(), n_items * sizeof(int), cudaMemcpyHostToDevice));
-    MCFD_CUDA(ctx, cudaMemcpy(pe.item_neighbour.p, item_nbr.data(), n_items * sizeof(int), cudaMemcpyHostToDevice));
-  }
-  if (n_neighbours) {
-    MCFD_CUDA(ctx, cudaMemcpy(pe.state_dev.p, st.data(), st.size() * sizeof(double *), cudaMemcpyHostToDevice));
-    MCFD_CUDA(ctx, cudaMemcpy(pe.flag_dev.p, fl.data(), fl.size() * sizeof(void *), cudaMemcpyHostToDevice));
-  }
+  MCFD_CUDA(ctx, cudaMemcpy(pe.flag_dev.p, fl.data(), fl.size() * sizeof(void *), cudaMemcpyHostToDevice));
   MCFD_CUDA(ctx, cudaMemcpy(pe.dt_slot_dev.p, ds.data(), world * sizeof(double *), cudaMemcpyHostToDevice));
   MCFD_CUDA(ctx, cudaMemcpy(pe.dt_flag_dev.p, df.data(), world * sizeof(void *), cudaMemcpyHostToDevice));
+  if (!ctx->dt_dev.p) MCFD_CUDA(ctx, ctx->dt_dev.Alloc(1));   // not inside a step: cudaMalloc may wait for kernels that poll
   if (!pe.side) {
     int lo = 0, hi = 0;
     MCFD_CUDA(ctx, cudaDeviceGetStreamPriorityRange(&lo, &hi));
     MCFD_CUDA(ctx, cudaStreamCreateWithPriority(&pe.side, cudaStreamNonBlocking, hi));
     MCFD_CUDA(ctx, cudaEventCreateWithFlags(&pe.ev_main, cudaEventDisableTiming));
     MCFD_CUDA(ctx, cudaEventCreateWithFlags(&pe.ev_side, cudaEventDisableTiming));
+    for (auto &e : pe.ev_copy) MCFD_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   }
   pe.rank = rank;
   pe.n_neighbours = n_neighbours;
   pe.connected = true;
   return MCFD_OK;
+}
+
+// id of the stream capture `stream` is part of, 0 when it is not capturing
+static unsigned long long CaptureId(cudaStream_t stream) {
+  cudaStreamCaptureStatus status = cudaStreamCaptureStatusNone;
+  unsigned long long id = 0;
+  if (cudaStreamGetCaptureInfo(stream, &status, &id) != cudaSuccess || status != cudaStreamCaptureStatusActive) return 0;
+  return id;
+}
+
+// the node-line stage kernel packs its send cells and waits for its ghost states itself
+static bool PeerIsFused(const mcfd_ctx *ctx) {
+  return ctx->use_lines && ctx->peer.n_neighbours > 0 && ctx->first_inter < ctx->mesh.n_local;
 }
 
 static int RequirePeer(mcfd_ctx *ctx) {
@@ -1240,38 +1275,79 @@ static int RequirePeer(mcfd_ctx *ctx) {
   return MCFD_OK;
 }
 
-int mcfd_peer_push(mcfd_ctx *ctx) {
-  if (int s = RequirePeer(ctx)) return s;
+static double *PeerStage3(DevBuf<double> &b, int buf) { return b.p + (size_t)buf * (b.n / 3); }
+
+// steps 2 and 3 of a delivery (peer.cuh): the copies of send stage `buf` into the neighbours' receive stages `buf`,
+// then the signal.  add: the host's part of the count; bump_plain: this is a delivery by mcfd_peer_push.
+static int PeerCopyAndSignal(mcfd_ctx *ctx, cudaStream_t stream, int buf, int bump_plain, int add) {
   auto &pe = ctx->peer;
-  const int buf = ctx->rk_order ? ctx->rk_in : ctx->cur;
-  ++pe.halo_epoch;
-  const int n_items = (int)ctx->send_cells.n;
-  if (pe.n_neighbours == 0) return MCFD_OK;
-  const int threads = 128;
-  const dim3 grid((unsigned)std::max(1, (n_items + threads - 1) / threads), (unsigned)std::min(ctx->fields, 27));
-  PeerPushKernel<<<grid, threads, 0, ctx->stream>>>(ctx->u[buf].p, ctx->fields, ctx->send_cells.p, pe.dest_cells.p,
-      pe.item_neighbour.p, n_items, pe.state_dev.p, buf, pe.flag_dev.p, pe.n_neighbours, pe.halo_epoch, pe.done.p);
+  const size_t n_send = ctx->send_cells.n;
+  const double *from = PeerStage3(pe.send_stage, buf);
+  for (int i = 0; i < pe.n_neighbours; ++i) {
+    const size_t count = (size_t)ctx->send_counts[i];
+    if (!count) continue;
+    double *to = pe.nbr_recv[i] + (size_t)buf * (size_t)pe.nbr_recv_total[i] * ctx->fields;
+    MCFD_CUDA(ctx, cudaMemcpy2DAsync(to, (size_t)pe.nbr_recv_total[i] * sizeof(double), from + pe.send_offset[i],
+        n_send * sizeof(double), count * sizeof(double), (size_t)ctx->fields, cudaMemcpyDeviceToDevice, stream));
+  }
+  PeerSignalKernel<<<1, kPeerMaxNeighbours, 0, stream>>>(pe.flag_dev.p, pe.n_neighbours, pe.counts.p, bump_plain, add);
   MCFD_CUDA(ctx, cudaGetLastError());
   ctx->launches++;
   return MCFD_OK;
+}
+
+static int LaunchPeerPack(mcfd_ctx *ctx, cudaStream_t stream, int buf) {
+  auto &pe = ctx->peer;
+  const int n = (int)ctx->send_cells.n;
+  if (!n) return MCFD_OK;
+  const long long work = (long long)n * ctx->fields;
+  PeerPackKernel<<<(int)std::min<long long>(1184, (work + 255) / 256), 256, 0, stream>>>(ctx->u[buf].p, ctx->fields,
+      ctx->send_cells.p, n, PeerStage3(pe.send_stage, buf));
+  MCFD_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  return MCFD_OK;
+}
+static int LaunchPeerUnpack(mcfd_ctx *ctx, cudaStream_t stream, int buf) {
+  auto &pe = ctx->peer;
+  const int n = (int)ctx->recv_cells.n;
+  if (!n) return MCFD_OK;
+  const long long work = (long long)n * ctx->fields;
+  PeerUnpackKernel<<<(int)std::min<long long>(1184, (work + 255) / 256), 256, 0, stream>>>(ctx->u[buf].p, ctx->fields,
+      ctx->recv_cells.p, n, PeerStage3(pe.recv_stage, buf));
+  MCFD_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  return MCFD_OK;
+}
+
+int mcfd_peer_push(mcfd_ctx *ctx) {
+  if (int s = RequirePeer(ctx)) return s;
+  auto &pe = ctx->peer;
+  pe.pushed_once = true;
+  if (pe.n_neighbours == 0) return MCFD_OK;
+  const int buf = ctx->rk_order ? ctx->rk_in : ctx->cur;
+  if (int s = LaunchPeerPack(ctx, ctx->stream, buf)) return s;
+  // the count goes on from the stage deliveries of the last step, which the device adds up at the next step only
+  return PeerCopyAndSignal(ctx, ctx->stream, buf, 1, pe.deliveries_this_step);
 }
 
 int mcfd_peer_wait(mcfd_ctx *ctx) {
   if (int s = RequirePeer(ctx)) return s;
   auto &pe = ctx->peer;
   if (pe.n_neighbours == 0) return MCFD_OK;
-  if (pe.halo_epoch == 0) return Fail(ctx, MCFD_ERR_STATE, "nothing has been pushed yet (mcfd_peer_push)");
-  PeerWaitKernel<<<1, kPeerMaxNeighbours, 0, ctx->stream>>>(pe.flags.p, pe.n_neighbours, pe.halo_epoch, pe.error.p);
+  if (!pe.pushed_once) return Fail(ctx, MCFD_ERR_STATE, "nothing has been pushed yet (mcfd_peer_push)");
+  const int buf = ctx->rk_order ? ctx->rk_in : ctx->cur;
+  PeerWaitKernel<<<1, kPeerMaxNeighbours, 0, ctx->stream>>>(pe.flags.p, pe.n_neighbours, pe.counts.p,
+      pe.deliveries_this_step, pe.error.p);
   MCFD_CUDA(ctx, cudaGetLastError());
   ctx->launches++;
-  return MCFD_OK;
+  return LaunchPeerUnpack(ctx, ctx->stream, buf);
 }
 
 static int PeerDtPublish(mcfd_ctx *ctx, double *dt_dev) {
   auto &pe = ctx->peer;
-  ++pe.dt_epoch;
-  PeerDtPublishKernel<<<1, kPeerMaxRanks, 0, ctx->stream>>>(dt_dev, pe.rank, pe.world, (int)(pe.dt_epoch & 1),
-      pe.dt_slot_dev.p, pe.dt_flag_dev.p, pe.dt_epoch);
+  PeerDtPublishKernel<<<1, kPeerMaxRanks, 0, ctx->stream>>>(dt_dev, pe.rank, pe.world, pe.dt_slot_dev.p,
+      pe.dt_flag_dev.p, pe.counts.p, pe.deliveries_this_step);
+  pe.deliveries_this_step = 0;
   MCFD_CUDA(ctx, cudaGetLastError());
   ctx->launches++;
   return MCFD_OK;
@@ -1279,7 +1355,7 @@ static int PeerDtPublish(mcfd_ctx *ctx, double *dt_dev) {
 static int PeerDtReduce(mcfd_ctx *ctx, double *dt_dev) {
   auto &pe = ctx->peer;
   PeerDtReduceKernel<<<1, kPeerMaxRanks, 0, ctx->stream>>>(pe.flags.p + kPeerMaxNeighbours, pe.dt_slots.p, pe.world,
-      (int)(pe.dt_epoch & 1), pe.dt_epoch, dt_dev, pe.error.p);
+      pe.counts.p, dt_dev, pe.error.p);
   MCFD_CUDA(ctx, cudaGetLastError());
   ctx->launches++;
   return MCFD_OK;
@@ -1292,8 +1368,9 @@ int mcfd_peer_min_time_step(mcfd_ctx *ctx, double *dt_dev) {
   return PeerDtReduce(ctx, dt_dev);
 }
 
-// One stage of an open RK step: the inner cells on the caller's stream (fem.hpp:249-254) while the high-priority side
-// stream waits for the ghost rows, advances the inter cells (fem.hpp:255-256) and at once sends their new values on.
+// One stage of an open RK step with the stage kernels that read ghost ROWS: the inner cells on the caller's stream
+// (fem.hpp:249-254) while the high-priority side stream waits for the delivery, unpacks it, advances the inter cells
+// (fem.hpp:255-256) and at once delivers their new values.
 static int PeerStage(mcfd_ctx *ctx, int stage) {
   auto &pe = ctx->peer;
   cudaStream_t main = ctx->stream;
@@ -1303,7 +1380,9 @@ static int PeerStage(mcfd_ctx *ctx, int stage) {
   ctx->stream = pe.side;
   int status = mcfd_peer_wait(ctx);
   if (status == MCFD_OK) status = mcfd_rk_stage_inter(ctx, stage);
-  if (status == MCFD_OK) status = mcfd_peer_push(ctx);
+  const int buf = ctx->rk_order ? ctx->rk_in : ctx->cur;        // the stage's output
+  if (status == MCFD_OK) status = LaunchPeerPack(ctx, pe.side, buf);
+  if (status == MCFD_OK) status = PeerCopyAndSignal(ctx, pe.side, buf, 0, ++pe.deliveries_this_step);
   ctx->stream = main;
   if (status != MCFD_OK) return status;
   MCFD_CUDA(ctx, cudaEventRecord(pe.ev_side, pe.side));
@@ -1311,7 +1390,44 @@ static int PeerStage(mcfd_ctx *ctx, int stage) {
   return MCFD_OK;
 }
 
-// Several contexts driven by this thread (one per GPU, or several on one GPU) advance in lockstep: every push is
+// The same stage with the node-line kernel: ONE launch over all blocks on the caller's stream (StageArgs::PeerStage:
+// its inter-cell blocks, the last ones, wait for the delivery themselves, read the ghost states from the receive
+// stage and leave a packed copy of the send cells), and behind it, on the side stream, the copies and the signal.
+static int PeerFusedStage(mcfd_ctx *ctx, int stage) {
+  auto &pe = ctx->peer;
+  if (!ctx->rk_order || stage < 0 || stage >= ctx->rk_order) return Fail(ctx, MCFD_ERR_STATE, "no such stage in the open RK step");
+  int in, out, mode;
+  StageBuffers(ctx, stage, &in, &out, &mode);
+  if (in != ctx->rk_in) return Fail(ctx, MCFD_ERR_STATE, "stages must be run in order");
+  if (ctx->time_cb) ctx->time_cb(ctx->time_user, mcfd_rk_stage_time(ctx, stage));
+  StageArgs::PeerStage f{};
+  f.on = 1;
+  f.first_block = (int)(ctx->first_inter / ctx->cpb);
+  f.first_cell = (int)ctx->first_inter;
+  f.n_neighbours = pe.n_neighbours;
+  f.wait_add = pe.deliveries_this_step;
+  f.n_send = (int)ctx->send_cells.n; f.n_recv = (int)ctx->recv_cells.n;
+  f.flags = pe.flags.p; f.counts = pe.counts.p;
+  f.recv = PeerStage3(pe.recv_stage, in); f.recv_index = pe.recv_index.p;
+  f.send = PeerStage3(pe.send_stage, out); f.tgt_offset = pe.tgt_offset.p; f.tgt_item = pe.tgt_item.p;
+  f.error = pe.error.p;
+  cudaStream_t main = ctx->stream;
+  // The copies that last read this send stage, two stages ago.  An event recorded outside the capture under way (or in
+  // one that is over) cannot be waited for and need not be: graph launches and plain work on a stream do not overlap.
+  if (pe.ev_copy_capture[out] == CaptureId(main)) MCFD_CUDA(ctx, cudaStreamWaitEvent(main, pe.ev_copy[out], 0));
+  if (int s = LaunchStage(ctx, ctx->u[in].p, ctx->u[ctx->rk_u0].p, ctx->u[out].p, mode, ctx->rk_dt, 0, ctx->total_blocks, &f))
+    return s;
+  MCFD_CUDA(ctx, cudaEventRecord(pe.ev_main, main));
+  MCFD_CUDA(ctx, cudaStreamWaitEvent(pe.side, pe.ev_main, 0));
+  if (int s = PeerCopyAndSignal(ctx, pe.side, out, 0, ++pe.deliveries_this_step)) return s;
+  MCFD_CUDA(ctx, cudaEventRecord(pe.ev_copy[out], pe.side));
+  pe.ev_copy_capture[out] = CaptureId(main);
+  ctx->rk_in = out;
+  if (stage == ctx->rk_order - 1) { ctx->cur = out; ctx->rk_order = 0; }
+  return MCFD_OK;
+}
+
+// Several contexts driven by this thread (one per GPU, or several on one GPU) advance in lockstep: every delivery is
 // enqueued before any wait that depends on it, whatever streams and hardware queues the contexts share.
 int mcfd_peer_step_group(mcfd_ctx *const *ctxs, int32_t n, int order, double t, double dt_guess) {
   if (!ctxs || n < 1) return MCFD_ERR_ARG;
@@ -1326,7 +1442,7 @@ int mcfd_peer_step_group(mcfd_ctx *const *ctxs, int32_t n, int order, double t, 
   int status = MCFD_OK;
   for (int c = 0; c < n && !status; ++c) {   // the ghost images of a solution that has never been sent
     on(ctxs[c]);
-    if (ctxs[c]->peer.halo_epoch == 0) status = mcfd_peer_push(ctxs[c]);
+    if (!ctxs[c]->peer.pushed_once) status = mcfd_peer_push(ctxs[c]);
   }
   for (int c = 0; c < n && !status; ++c) {
     on(ctxs[c]);
@@ -1341,7 +1457,7 @@ int mcfd_peer_step_group(mcfd_ctx *const *ctxs, int32_t n, int order, double t, 
   for (int stage = 0; stage < order && !status; ++stage)
     for (int c = 0; c < n && !status; ++c) {
       on(ctxs[c]);
-      status = PeerStage(ctxs[c], stage);
+      status = PeerIsFused(ctxs[c]) ? PeerFusedStage(ctxs[c], stage) : PeerStage(ctxs[c], stage);
     }
   if (status) for (int c = 0; c < n; ++c) ctxs[c]->rk_order = 0;
   cudaSetDevice(dev0);
@@ -1352,13 +1468,21 @@ int mcfd_peer_step(mcfd_ctx *ctx, int order, double t, double dt_guess) {
   return mcfd_peer_step_group(&ctx, 1, order, t, dt_guess);
 }
 
+int mcfd_peer_join(mcfd_ctx *ctx) {
+  if (int s = RequirePeer(ctx)) return s;
+  auto &pe = ctx->peer;
+  MCFD_CUDA(ctx, cudaEventRecord(pe.ev_side, pe.side));
+  MCFD_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, pe.ev_side, 0));
+  return MCFD_OK;
+}
+
 int mcfd_peer_check(mcfd_ctx *ctx) {
   if (int s = RequirePeer(ctx)) return s;
   MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   MCFD_CUDA(ctx, cudaStreamSynchronize(ctx->peer.side));
   int err = 0;
   MCFD_CUDA(ctx, cudaMemcpy(&err, ctx->peer.error.p, sizeof(int), cudaMemcpyDeviceToHost));
-  if (err) return Fail(ctx, MCFD_ERR_STATE, "a neighbour's data did not arrive within the polling limit");
+  if (err) return Fail(ctx, MCFD_ERR_STATE, "a neighbour's delivery did not arrive within the polling limit");
   return MCFD_OK;
 }
 

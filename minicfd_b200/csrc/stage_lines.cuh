@@ -358,8 +358,14 @@ MCFD_HD void LineStageNeighbour(const StageArgs &p, const LineThread<Q, CPB> &g,
   const int nb = g.sNbr[f * CPB + g.lc], code = g.sCode[f * CPB + g.lc];
   if (nb < 0) return;
   const int n2node = g.sNbrNode[((code & 7) * 8 + ((code >> 3) & 7)) * S::FQ + q];
-  const double *src = p.u_in + ((size_t)(nb >> 5) * S::F + n2node * 5) * kTile + (nb & 31);
   double *dst = g.sN + (size_t)((f * S::FQ + q) * 5) * CPB + g.lc;
+  if (p.peer.on && nb >= p.n_local) {   // a ghost cell whose state lies in the receive stage [row][item] (peer.cuh)
+    const double *src = p.peer.recv + (size_t)(n2node * 5) * p.peer.n_recv + p.peer.recv_index[nb - p.n_local];
+#pragma unroll
+    for (int c = 0; c < 5; ++c) AsyncCopy8(dst + c * CPB, src + (size_t)c * p.peer.n_recv);
+    return;
+  }
+  const double *src = p.u_in + ((size_t)(nb >> 5) * S::F + n2node * 5) * kTile + (nb & 31);
 #pragma unroll
   for (int c = 0; c < 5; ++c) AsyncCopy8(dst + c * CPB, src + c * kTile);
 }
@@ -609,7 +615,7 @@ MCFD_HD void LinePhaseN(const StageArgs &p, const LineTables &tab, int tid, int 
   const double *own = g.sF + (size_t)n0 * ND * CPB + lc;
   const LineJacobian J = ComputeLineJacobian(g.sG + lc, CPB, tab.xi[i], tab.xi[j]);
   const double cF = tab.coef_F;
-  double a0[Q], a1[Q];
+  double a0[Q], a1[Q], out[Q][5];
 #pragma unroll
   for (int m = 0; m < Q; ++m) {
     a0[m] = tab.a[i][m] + ((m == i && i_end) ? (i == 0 ? -cF : cF) : 0.0);
@@ -654,7 +660,19 @@ MCFD_HD void LinePhaseN(const StageArgs &p, const LineTables &tab, int tid, int 
       const double sum = fma(ld.u0[k][c], c0, w * cw);
       const double qv = sum * cs;
       const double val = fma(fma(-cs_inv, qv, sum), cs, qv);
-      p.u_out[row0 + (k * 5 + c) * kTile] = mode == kModeResidual ? res : val;
+      out[k][c] = mode == kModeResidual ? res : val;
+      p.u_out[row0 + (k * 5 + c) * kTile] = out[k][c];
+    }
+  }
+  if (p.peer.on && g.cell >= p.peer.first_cell) {   // a second copy of a send cell's rows, packed for the copy engines
+    const int t0 = p.peer.tgt_offset[g.cell - p.peer.first_cell], t1 = p.peer.tgt_offset[g.cell - p.peer.first_cell + 1];
+    for (int tt = t0; tt < t1; ++tt) {
+      double *to = p.peer.send + (size_t)n0 * 5 * p.peer.n_send + p.peer.tgt_item[tt];
+#pragma unroll
+      for (int k = 0; k < Q; ++k) {
+#pragma unroll
+        for (int c = 0; c < 5; ++c) to[(size_t)(k * 5 + c) * p.peer.n_send] = out[k][c];
+      }
     }
   }
 }
@@ -665,6 +683,12 @@ __global__ void __maxnreg__((LineShape<Q, CPB>::kMaxRegs))
 LineStageKernel(const __grid_constant__ StageArgs p, const __grid_constant__ LineTables tab) {
   extern __shared__ double smem[];
   const int tid = threadIdx.x, bid = blockIdx.x;
+  if (p.peer.on && p.block_begin + bid >= p.peer.first_block) {   // a block with inter cells: the neighbours' delivery
+    if (tid < p.peer.n_neighbours &&
+        !SpinUntil(p.peer.flags + tid, p.peer.counts[kPeerPlain] + p.peer.counts[kPeerStageBase] + (unsigned long long)p.peer.wait_add))
+      *p.peer.error = 1;
+    __syncthreads();
+  }
   LineRegs<Q> t;
   LineLoad<Q, CPB>(p, tab, tid, bid, smem, &t);
   LinePrologue<Q, CPB>(p, tab, tid, bid, smem);

@@ -98,7 +98,7 @@ int emu_stage(int degree, int scheme, int riemann, int64_t n_nodes, const double
     for (int f = 0; f < F; ++f) uin[((c >> 5) * F + f) * kTile + (c & 31)] = column_in[c * F + f];
   for (int64_t c = 0; c < n_local; ++c)
     for (int f = 0; f < F; ++f) u0[((c >> 5) * F + f) * kTile + (c & 31)] = column_u0[c * F + f];
-  StageArgs a;
+  StageArgs a{};
   a.u_in = uin.data(); a.u0 = u0.data(); a.u_out = uout.data();
   a.geom = geom.data(); a.nbr = nbr.data(); a.code = code.data();
   a.bkind = bkind.data(); a.bvals = bvals ? bvals : zero_vals.data();
@@ -267,7 +267,7 @@ static void RunEnergy(HostMesh const &mesh, const double *betas, const double *c
   std::vector<double> bvals((mesh.bound_faces.size() + 1) * Q * Q * 5, 0.0);
   std::vector<double> u((size_t)nt * F * kTile, 0.0), res(u.size(), 0.0), grad((size_t)nt * N * 15 * kTile, 0.0),
       hn((size_t)nt * 6 * Q * Q * 15 * kTile, 0.0), damping((size_t)nt * N * N * kTile, 0.0), smem(G::kSharedBytes / 8 + 1);
-  StageArgs a;
+  StageArgs a{};
   a.u_in = u.data(); a.u0 = u.data(); a.u_out = res.data(); a.geom = geom.data(); a.nbr = nbr.data(); a.code = code.data();
   a.bkind = bkind.data(); a.bvals = bvals.data(); a.n_local = (int)nl; a.block_begin = 0; a.mode = kModeResidual; a.dt = 0;
   a.dt_dev = nullptr; a.grad = grad.data(); a.hn = hn.data(); a.h2s = h2s.data(); a.cell_nu = nullptr;

@@ -23,8 +23,15 @@ sp.ctx.set_stream(torch.cuda.current_stream().cuda_stream)
 sp.Approximate(lambda x: fields.vortex()(x, 0.0))
 if comm: comm.exchange()
 rk = RungeKutta(3); dt_dev = torch.zeros(1, dtype=torch.float64, device="cuda")
+use_peer = world > 1 and "--nccl" not in sys.argv
+if use_peer:
+    from minicfd_b200 import peer
+    peer.connect(sp, part)
 def step():
-    time_step_device(sp, 1.0, 3, dt_dev); rk.UpdateDevice(sp, 0.0, dt_dev.data_ptr())
+    if use_peer:
+        sp.ctx.peer_step(3, 0.0, 1.0)
+    else:
+        time_step_device(sp, 1.0, 3, dt_dev); rk.UpdateDevice(sp, 0.0, dt_dev.data_ptr())
 for _ in range(5): step()
 torch.cuda.synchronize()
 if world > 1: dist.barrier()
@@ -36,6 +43,6 @@ if rank == 0:
     ev.sort(key=lambda e: e.time_range.start)
     t0 = ev[0].time_range.start
     for e in ev:
-        print(f"{e.time_range.start - t0:9.1f} us  +{e.time_range.elapsed_us():8.1f}  {e.name[:70]}")
+        print(f"{e.time_range.start - t0:9.1f} us  +{e.time_range.elapsed_us():8.1f}  stream {getattr(e, 'stream', '?')}  {e.name[:70]}")
 if world > 1:
     comm.drain(); torch.cuda.synchronize(); dist.destroy_process_group()
