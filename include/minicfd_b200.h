@@ -310,6 +310,12 @@ int mcfd_time_step(mcfd_ctx *ctx, double dt_guess, int rk_order, double *dt_loca
  * left in device memory (dt_dev, or an internal scalar when NULL), may be min-reduced across ranks there
  * (ncclAllReduce MIN = the MPI_Allreduce of demo/euler/sourceless.cpp:194), and the RK stage kernels read
  * it from there.  Nothing synchronises the stream. */
+/* The stage times t + dt and t + dt / 2 (rk.hpp:24-47) are not known to the host then.  A context whose boundary
+ * values depend on time (mcfd_set_time_dependent(ctx, 1): its time callback re-samples them per stage) therefore
+ * refuses mcfd_rk_begin_device / mcfd_rk_step_device / mcfd_peer_step for orders above one with MCFD_ERR_STATE;
+ * read the step back with mcfd_time_step and use mcfd_rk_step.  Without that flag the callback is still called,
+ * with the time of the step's beginning for every stage. */
+int mcfd_set_time_dependent(mcfd_ctx *ctx, int flag);
 int mcfd_time_step_device(mcfd_ctx *ctx, double dt_guess, int rk_order, double *dt_dev);
 int mcfd_rk_begin_device(mcfd_ctx *ctx, int order, double t, const double *dt_dev);
 int mcfd_rk_step_device(mcfd_ctx *ctx, int order, double t, const double *dt_dev);
@@ -318,8 +324,11 @@ int mcfd_rk_step_device(mcfd_ctx *ctx, int order, double t, const double *dt_dev
  * (a host that gave the whole GPU to its own memory pool, a rank held to a fixed memory budget, a time
  * loop that must not meet the device-wide synchronisation hidden in cudaMalloc/cudaFree).  No counterpart
  * in the reference: its GetTimeStep (fem.hpp:417-435) runs on host memory it already owns.
- * It needs no context and calls no allocator of any kind: inputs and output are the caller's device memory —
- * column_dev: the solution column [n_cells][N][5] (reference layout); length_dev: Cell::length() of
+ * It needs no context and allocates no device memory, pinned memory or stream (only a failing call touches the host
+ * heap, for its error message): inputs and output are the caller's device memory —
+ * column_dev: the solution column [n_cells][N][5] in the reference layout of expansions with kLocal == false, i.e.
+ * the nodal values u themselves (a kLocal == true column holds det(J) u and would give a wrong wave speed: divide
+ * first); length_dev: Cell::length() of
  * each cell (mcfd_get_cell_geometry); dt_dev: one double receiving the part-local time step.  The
  * reduction's scratch is a fixed 1 MiB array inside the library image, held by every GPU that loads
  * the library until the process ends; it limits a call to 1 048 576 cells and larger n_cells are refused

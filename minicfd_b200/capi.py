@@ -74,6 +74,7 @@ SYMBOLS = {
     "mcfd_format_integers": (C.c_int, [_P, C.c_int64, C.c_int64, C.c_int64, C.c_char_p, C.c_int64, _I64]),
     "mcfd_project": (C.c_int, [_P, _D]),
     "mcfd_set_time_callback": (C.c_int, [_P, TIME_CALLBACK, _P]),
+    "mcfd_set_time_dependent": (C.c_int, [_P, C.c_int]),
     "mcfd_count_local_cells": (C.c_int64, [_P]),
     "mcfd_cell_data_size": (C.c_int64, [_P]),
     "mcfd_set_solution": (C.c_int, [_P, _D]),
@@ -332,6 +333,9 @@ class Context:
         return (sp.value or 0, sn.value), (rp.value or 0, rn.value)
 
     # ---- halo through peer-mapped memory (mcfd_peer_*) ----
+    def set_time_dependent(self, flag):
+        self._check(self.lib.mcfd_set_time_dependent(self.h, 1 if flag else 0))
+
     def peer_export(self, world):
         """-> (three 64-byte IPC handles, three device pointers): epoch words, time-step slots, receive stage."""
         handles = (C.c_ubyte * (3 * 64))()

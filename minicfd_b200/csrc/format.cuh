@@ -115,7 +115,7 @@ MCFD_HD Token FormatInteger(long long v) {   // operator<<(integer) and a blank
   char tmp[24];
   int m = 0, n = 0;
   unsigned long long u = v < 0 ? 0ull - (unsigned long long)v : (unsigned long long)v;
-  do { tmp[m++] = (char)('0' + u % 10); u /= 10; } while (u && m < 14);
+  do { tmp[m++] = (char)('0' + u % 10); u /= 10; } while (u && m < 14);   // mcfd_format_integers refuses 10^14 and more
   if (v < 0) t.c[n++] = '-';
   while (m) t.c[n++] = tmp[--m];
   t.c[n++] = ' ';

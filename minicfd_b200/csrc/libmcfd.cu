@@ -21,6 +21,14 @@ namespace {
 
 thread_local std::string g_create_error;
 
+// "this function's attributes have been set" — per device: cudaFuncSetAttribute applies to the current device only
+struct DeviceFlags {
+  bool done[64] = {false};
+  static int Current() { int d = 0; cudaGetDevice(&d); return (d >= 0 && d < 64) ? d : 0; }
+  bool Here() const { return done[Current()]; }
+  void Set() { done[Current()] = true; }
+};
+
 template <class T>
 struct DevBuf {
   T *p = nullptr;
@@ -45,6 +53,8 @@ struct mcfd_ctx {
   mcfd_config cfg{};
   int q = 3, n_nodes = 27, fields = 135;
   int cpb = 32, n_warps = 9;
+  int device = 0;                               // the device the context lives on; made current by every call
+  bool time_dependent = false;                  // some boundary value depends on time (mcfd_set_time_dependent)
   cudaStream_t stream = nullptr;
   std::string error;
   Tables tables{};
@@ -131,10 +141,13 @@ int Fail(mcfd_ctx *ctx, int status, std::string msg) {
   return status;
 }
 
-// The per-degree tables live in ONE __constant__ symbol per device while every context owns its own copy
-// (degree, scheme, launch shape and Vincent parameter differ between contexts).  Before a context launches a
-// kernel that reads them, the symbol is brought in line with that context, stream-ordered on the context's
-// stream.  Contexts with different tables must therefore not run kernels concurrently on different streams.
+// The kernels other than the node-line stage kernel (whose tables are a kernel parameter) read the per-degree tables
+// from ONE __constant__ symbol per device, while every context owns its own copy (degree, scheme, launch shape and
+// Vincent parameter differ between contexts).  Before a context launches such a kernel the symbol is brought in line
+// with it.  A switch waits for everything in flight on the device (kernels of the other shape may still be reading the
+// old constants, on any stream) and is complete before the call returns (whatever stream the context uses next finds
+// the new ones): contexts of different shape may be used in turn on any streams; they take turns on the device.
+// Not during stream capture — run a step of the context first.
 Tables g_device_tables[64];
 bool g_device_tables_valid[64] = {false};
 
@@ -145,7 +158,12 @@ cudaError_t EnsureTables(mcfd_ctx *ctx) {
   if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
   if (g_device_tables_valid[dev] && std::memcmp(&g_device_tables[dev], &ctx->tables, sizeof(Tables)) == 0)
     return cudaSuccess;
-  e = cudaMemcpyToSymbolAsync(c_tab, &ctx->tables, sizeof(Tables), 0, cudaMemcpyHostToDevice, ctx->stream);
+  g_device_tables_valid[dev] = false;
+  e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) return e;
+  e = cudaMemcpyToSymbol(c_tab, &ctx->tables, sizeof(Tables), 0, cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) return e;
+  e = cudaDeviceSynchronize();
   if (e != cudaSuccess) return e;
   g_device_tables[dev] = ctx->tables;
   g_device_tables_valid[dev] = true;
@@ -163,11 +181,11 @@ template <int Q, int R, int CPB, int NW, bool kGeneral, int kViscous = kDiffNone
 cudaError_t LaunchStageG(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
   size_t smem = StageGeometry<Q, CPB, NW>::kSharedBytes;
   auto kernel = StageKernel<Q, R, CPB, NW, kGeneral, kViscous>;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceFlags configured;
+  if (!configured.Here()) {
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    configured = true;
+    configured.Set();
   }
   kernel<<<n_blocks, NW * 32, smem, ctx->stream>>>(a);
   return cudaGetLastError();
@@ -178,12 +196,15 @@ template <int Q, int R, int CPB>
 cudaError_t LaunchLineR(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
   using S = LineShape<Q, CPB>;
   auto kernel = LineStageKernel<Q, R, CPB>;
-  // per device, not per process: the attribute belongs to the current device's copy of the function
-  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::kSharedBytes);
-  if (e != cudaSuccess) return e;
-  // all of the SM's shared memory: the default carve-out holds one CTA of this size, the kernel is built for kMinBlocks
-  e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-  if (e != cudaSuccess) return e;
+  static DeviceFlags configured;
+  if (!configured.Here()) {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::kSharedBytes);
+    if (e != cudaSuccess) return e;
+    // all of the SM's shared memory: the default carve-out holds one CTA of this size, the kernel is built for kMinBlocks
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (e != cudaSuccess) return e;
+    configured.Set();
+  }
   kernel<<<n_blocks, S::kThreads, S::kSharedBytes, ctx->stream>>>(a, ctx->line_tables);
   return cudaGetLastError();
 }
@@ -250,22 +271,22 @@ int LaunchTrace(mcfd_ctx *ctx, const double *u, int64_t cell_begin, int64_t cell
     e = cudaGetLastError();
   } else if (ctx->cfg.k_local) {
     auto kernel = TraceKernel<4, true>;
-    static bool configured = false;
-    if (!configured) {
+    static DeviceFlags configured;
+    if (!configured.Here()) {
       e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TraceShape<4>::kSharedBytes);
       if (e != cudaSuccess) return Fail(ctx, MCFD_ERR_CUDA, cudaGetErrorString(e));
-      configured = true;
+      configured.Set();
     }
     kernel<<<tile_end - tile_begin, TraceShape<4>::NW * 32, TraceShape<4>::kSharedBytes, ctx->stream>>>(u, ctx->geom.p, ctx->grad.p,
         ctx->hn.p, tile_begin, (int)cell_begin, (int)cell_end);
     e = cudaGetLastError();
   } else {
     auto kernel = TraceKernel<4>;
-    static bool configured = false;
-    if (!configured) {
+    static DeviceFlags configured;
+    if (!configured.Here()) {
       e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TraceShape<4>::kSharedBytes);
       if (e != cudaSuccess) return Fail(ctx, MCFD_ERR_CUDA, cudaGetErrorString(e));
-      configured = true;
+      configured.Set();
     }
     kernel<<<tile_end - tile_begin, TraceShape<4>::NW * 32, TraceShape<4>::kSharedBytes, ctx->stream>>>(u, ctx->geom.p, ctx->grad.p,
         ctx->hn.p, tile_begin, (int)cell_begin, (int)cell_end);
@@ -371,11 +392,11 @@ int LaunchConvert(mcfd_ctx *ctx, double *tiles, double *column, const int *cells
     constexpr int F = 320;
     size_t smem = (size_t)kTile * (F + 1) * sizeof(double);
     auto kernel = ConvertKernel<F, kToTiles>;
-    static bool configured = false;
-    if (!configured) {
+    static DeviceFlags configured;
+    if (!configured.Here()) {
       e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (e != cudaSuccess) return Fail(ctx, MCFD_ERR_CUDA, cudaGetErrorString(e));
-      configured = true;
+      configured.Set();
     }
     kernel<<<blocks, 256, smem, ctx->stream>>>(tiles, column, cells, (int)n_items);
     e = cudaGetLastError();
@@ -410,6 +431,8 @@ int UnscaleTilesByDet(mcfd_ctx *ctx, double *tiles) {
 int RequireMesh(mcfd_ctx *ctx) {
   if (!ctx) return MCFD_ERR_ARG;
   if (!ctx->has_mesh) return Fail(ctx, MCFD_ERR_STATE, "mcfd_set_mesh has not been called");
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev != ctx->device) MCFD_CUDA(ctx, cudaSetDevice(ctx->device));
   return MCFD_OK;
 }
 
@@ -481,6 +504,8 @@ int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
   }
   auto ctx = std::make_unique<mcfd_ctx>();
   ctx->cfg = *config;
+  e = cudaGetDevice(&ctx->device);
+  if (e != cudaSuccess) return Fail(nullptr, MCFD_ERR_CUDA, cudaGetErrorString(e));
   ctx->q = config->degree + 1;
   ctx->n_nodes = ctx->q * ctx->q * ctx->q;
   ctx->fields = 5 * ctx->n_nodes;
@@ -534,6 +559,7 @@ int mcfd_set_mesh(mcfd_ctx *ctx, int64_t n_nodes, const double *xyz, int64_t n_l
   if (!ctx || !xyz || !cell_nodes || n_local <= 0 || n_ghost < 0)
     return Fail(ctx, MCFD_ERR_ARG, "bad mesh arguments");
   if (n_local + n_ghost > (int64_t)1 << 30) return Fail(ctx, MCFD_ERR_ARG, "too many cells for int32 ids");
+  MCFD_CUDA(ctx, cudaSetDevice(ctx->device));
   ctx->mesh = HostMesh();
   if (!ctx->global_ids.empty()) {
     if ((int64_t)ctx->global_ids.size() != n_local + n_ghost)
@@ -647,9 +673,14 @@ int mcfd_set_halo(mcfd_ctx *ctx, int32_t n_send_parts, const int64_t *send_count
     const int64_t *send_cells, int32_t n_recv_parts, const int64_t *recv_counts,
     const int64_t *recv_cells) {
   if (int s = RequireMesh(ctx)) return s;
+  if (n_send_parts < 0 || n_recv_parts < 0 || (n_send_parts && !send_counts) || (n_recv_parts && !recv_counts))
+    return Fail(ctx, MCFD_ERR_ARG, "bad halo lists");
   int64_t ns = 0, nr = 0;
   for (int i = 0; i < n_send_parts; ++i) ns += send_counts[i];
+  for (int i = 0; i < n_recv_parts; ++i) if (recv_counts[i] < 0) return Fail(ctx, MCFD_ERR_ARG, "negative halo count");
+  for (int i = 0; i < n_send_parts; ++i) if (send_counts[i] < 0) return Fail(ctx, MCFD_ERR_ARG, "negative halo count");
   for (int i = 0; i < n_recv_parts; ++i) nr += recv_counts[i];
+  if ((ns && !send_cells) || (nr && !recv_cells)) return Fail(ctx, MCFD_ERR_ARG, "null halo cell list");
   std::vector<int> s32(ns), r32(nr);
   for (int64_t i = 0; i < ns; ++i) {
     if (send_cells[i] < 0 || send_cells[i] >= ctx->mesh.n_local)
@@ -806,13 +837,13 @@ int mcfd_update_cell_viscosity(mcfd_ctx *ctx, double time_scale) {
   double *u = HaloState(ctx);
   TimeStepResetKernel<<<1, 1, 0, ctx->stream>>>(ctx->visc_dt_bits.p);
   const int nl = (int)ctx->mesh.n_local, tiles = (nl + kTile - 1) / kTile;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceFlags configured;
+  if (!configured.Here()) {
     MCFD_CUDA(ctx, cudaFuncSetAttribute(ViscosityKernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ViscosityShape<3>::kSharedBytes));
     MCFD_CUDA(ctx, cudaFuncSetAttribute(ViscosityKernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ViscosityShape<4>::kSharedBytes));
     MCFD_CUDA(ctx, cudaFuncSetAttribute(ViscosityKernel<3>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     MCFD_CUDA(ctx, cudaFuncSetAttribute(ViscosityKernel<4>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    configured = true;
+    configured.Set();
   }
   if (ctx->q == 3) ViscosityKernel<3><<<tiles, 160, ViscosityShape<3>::kSharedBytes, ctx->stream>>>(u, ctx->geom.p, ctx->nbr.p,
       ctx->code.p, ctx->damping.p, ctx->length.p, nl, time_scale, ctx->cell_nu.p, ctx->visc_dt_bits.p);
@@ -920,6 +951,12 @@ int mcfd_set_time_callback(mcfd_ctx *ctx, mcfd_time_callback fn, void *user) {
   return MCFD_OK;
 }
 
+int mcfd_set_time_dependent(mcfd_ctx *ctx, int flag) {
+  if (!ctx) return MCFD_ERR_ARG;
+  ctx->time_dependent = flag != 0;
+  return MCFD_OK;
+}
+
 int64_t mcfd_count_local_cells(const mcfd_ctx *ctx) {
   return (ctx && ctx->has_mesh) ? ctx->mesh.n_local : (int64_t)MCFD_ERR_STATE;
 }
@@ -1008,6 +1045,9 @@ int mcfd_rk_begin(mcfd_ctx *ctx, int order, double t, double dt) {
 
 int mcfd_rk_begin_device(mcfd_ctx *ctx, int order, double t, const double *dt_dev) {
   if (!dt_dev) return Fail(ctx, MCFD_ERR_ARG, "null dt_dev");
+  if (ctx && ctx->time_cb && ctx->time_dependent && order > 1)
+    return Fail(ctx, MCFD_ERR_STATE, "time-dependent boundary values need the stage times t + dt, t + dt / 2 on the host: "
+        "use mcfd_rk_begin / mcfd_rk_step with the time step read back (mcfd_time_step)");
   if (int s = mcfd_rk_begin(ctx, order, t, 0.0)) return s;
   ctx->rk_dt_dev = dt_dev;
   return MCFD_OK;
@@ -1512,15 +1552,15 @@ int WenoLazyBatch(mcfd_ctx *ctx, double *u, double w0, double eps, int64_t modal
     int64_t cell_begin, int64_t cell_end, bool publish, bool eigen) {
   constexpr int M = ModalShape<Q - 1>::M;
   const size_t smem = WenoShape<Q>::kSharedBytes;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceFlags configured;
+  if (!configured.Here()) {
     MCFD_CUDA(ctx, cudaFuncSetAttribute(ModalKernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     MCFD_CUDA(ctx, cudaFuncSetAttribute(WenoLazyKernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     MCFD_CUDA(ctx, cudaFuncSetAttribute(WenoEigenKernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     // several CTAs per SM only fit when the L1/shared split is asked for the shared side
     MCFD_CUDA(ctx, cudaFuncSetAttribute(ModalKernel<Q>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     MCFD_CUDA(ctx, cudaFuncSetAttribute(WenoLazyKernel<Q>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    configured = true;
+    configured.Set();
   }
   MCFD_CUDA(ctx, EnsureTables(ctx));
   if (modal_end > modal_begin) {   // Extrapolation::UpdateModalCoeff of the cells whose nodal values are new
@@ -1563,11 +1603,11 @@ int DgmWenoBatch(mcfd_ctx *ctx, double *u, double w0, double eps, int64_t taylor
     int64_t cell_begin, int64_t cell_end) {
   constexpr int M = ModalShape<Q - 1>::M;
   const size_t smem = WenoShape<Q>::kSharedBytes;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceFlags configured;
+  if (!configured.Here()) {
     MCFD_CUDA(ctx, cudaFuncSetAttribute(WenoLazyKernel<Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     MCFD_CUDA(ctx, cudaFuncSetAttribute(WenoLazyKernel<Q>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    configured = true;
+    configured.Set();
   }
   if (int s = LaunchDgmTaylor(ctx, u, taylor_begin, taylor_end)) return s;
   if (cell_end <= cell_begin) return MCFD_OK;
@@ -1823,6 +1863,10 @@ int mcfd_format_doubles(mcfd_ctx *ctx, int64_t n, const double *values, char *te
 int mcfd_format_integers(mcfd_ctx *ctx, int64_t n, int64_t first, int64_t step, char *text, int64_t capacity,
     int64_t *length) {
   if (!ctx) return MCFD_ERR_ARG;
+  // a token slot holds 14 digits, a sign and the blank
+  const long double last = (long double)first + (long double)step * (long double)(n > 0 ? n - 1 : 0);
+  if (std::fabs((double)first) >= 1e14 || std::fabs((double)last) >= 1e14)
+    return Fail(ctx, MCFD_ERR_ARG, "integers of 10^14 or more are not supported");
   return FormatAndPack(ctx, 1, nullptr, 0, n, first, step, text, capacity, length);
 }
 

@@ -408,6 +408,11 @@ struct HostMesh {
       int64_t n_pairs, const int64_t *pairs) {
     n_local = nl; n_ghost = ng;
     const int64_t nc = nl + ng;
+    // every node id must name a row of xyz: a malformed mesh is an error, not an out-of-bounds read
+    auto bad = [n_nodes](int64_t id) { return id < 0 || id >= n_nodes; };
+    for (int64_t k = 0; k < nc * 8; ++k) if (bad(cn[k])) { error = "cell " + std::to_string(k / 8) + " names node " + std::to_string(cn[k]) + " of " + std::to_string(n_nodes); return false; }
+    for (int64_t k = 0; k < n_bfaces * 4; ++k) if (bad(bf[k])) { error = "boundary face " + std::to_string(k / 4) + " names node " + std::to_string(bf[k]) + " of " + std::to_string(n_nodes); return false; }
+    for (int64_t k = 0; k < n_pairs * 8; ++k) if (bad(pairs[k])) { error = "periodic pair " + std::to_string(k / 8) + " names node " + std::to_string(pairs[k]) + " of " + std::to_string(n_nodes); return false; }
     // periodic identification: node of the second quad -> node of the first quad, per pair, applied
     // only to the face that carries it
     std::map<Key, std::array<int64_t, 8>> periodic;  // sorted key of B -> (B nodes, A nodes)

@@ -62,6 +62,8 @@ class Spatial:
     def _set_bc(self, tag, kind, func=None, time_dependent=True):
         self.ctx.set_boundary(tag, kind)
         self._bc_funcs[tag] = (kind, func, time_dependent)
+        # a device-resident time step (UpdateDevice, peer_step) cannot serve stage times to such a function
+        self.ctx.set_time_dependent(any(f is not None and td for _, f, td in self._bc_funcs.values()))
         if func is not None:
             self._bc_points[tag] = self.ctx.boundary_points(tag)
             self.ctx.set_boundary_values(tag, func(self._bc_points[tag], self._t))

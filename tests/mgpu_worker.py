@@ -88,7 +88,7 @@ def energy(sp, comm, m, parts, part, degree, rank, world):
         e_u = np.abs(sol.cpu().numpy() - u0).max() / np.abs(u0).max()
         e_n = np.abs(nus.cpu().numpy().reshape(-1, 5) - nu).max() / np.abs(nu).max()
         print(f"MGPU world={world} degree={degree} energy: solution rel err {e_u:.2e}, viscosity rel err {e_n:.2e}")
-        ok = e_u < 1e-11 and e_n < 1e-9
+        ok = e_u < 1e-12 and e_n < 1e-9
     finish(comm, ok, rank)
 
 
@@ -209,7 +209,7 @@ def main():
                 p.scatter_to_global(r.get_solution(k), kf, ref)
             e_u = np.abs(sol.cpu().numpy() - ref).max() / np.abs(ref).max()
             print(f"MGPU world={world} degree={degree} weno: solution rel err {e_u:.2e}")
-            ok = e_u < 1e-11
+            ok = e_u < 1e-12
         else:
             print("MGPU weno: reference binary not shipped, nothing to compare with")
     elif rank == 0:
@@ -228,7 +228,7 @@ def main():
         rref = o.residual(ref, tt)
         e_r = np.abs(res.cpu().numpy() - rref).max() / np.abs(rref).max()
         print(f"MGPU world={world} degree={degree}: solution rel err {e_u:.2e}, residual rel err {e_r:.2e}")
-        ok = e_u < 1e-12 and e_r < 1e-11 and frame_ok
+        ok = e_u < 1e-12 and e_r < 1e-12 and frame_ok
     finish(comm, ok, rank)
 
 

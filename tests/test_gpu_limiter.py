@@ -172,7 +172,7 @@ def test_weno_two_parts_with_halo_buffers_match_the_reference_parts():
             limit()
         t += 1e-3
     for k, sp in enumerate(S):
-        assert relerr(sp.GetSolutionColumn(), r.get_solution(k)) < 1e-11
+        assert relerr(sp.GetSolutionColumn(), r.get_solution(k)) < 1e-12
 
 
 # ---- weno::Eigen and EigenMatrices ------------------------------------------------------
@@ -190,7 +190,7 @@ def test_weno_eigen_golden(name, degree, riemann):
     assert np.array_equal(np.abs((got - g["u"]).reshape(-1, kf)).max(1) > 0, touched)   # same troubled cells
     assert relerr(got, g["limited"]) < TOL
     RungeKutta(3).Update(sp, 0.0, cases.GOLDEN_DT)
-    assert relerr(sp.GetSolutionColumn(), g["u_rk3"]) < 1e-11
+    assert relerr(sp.GetSolutionColumn(), g["u_rk3"]) < 1e-12
 
 
 @pytest.mark.parametrize("degree", [2, 3])

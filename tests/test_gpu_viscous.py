@@ -79,7 +79,7 @@ def test_navier_stokes_against_reference_binary_many_steps():
         RungeKutta(3).Update(sp, t, dt)
         t += dt
     r.rk_update(3, 0.0, dt, 10)
-    assert relerr(sp.GetSolutionColumn(), r.get_solution()) < 1e-11
+    assert relerr(sp.GetSolutionColumn(), r.get_solution()) < 1e-12
 
 
 def test_zero_viscosity_is_the_euler_path():
@@ -109,7 +109,7 @@ def test_viscous_free_stream_and_couette_like_shear():
         sp.SetSmartBoundary(tag, fields.constant(state))
     sp.Approximate(lambda x: fields.constant(state)(x, 0.0))
     res = sp.GetResidualColumn()
-    assert np.abs(res).max() < 1e-11
+    assert np.abs(res).max() < 1e-12
 
 
 def test_navier_stokes_two_parts_with_halo_buffers():
@@ -206,7 +206,7 @@ def test_energy_based_viscosity_golden(name, degree, riemann):
     sp.SetTime(cases.GOLDEN_T)
     assert relerr(sp.GetResidualColumn(), g["residual"]) < TOL
     RungeKutta(3).Update(sp, 0.0, cases.GOLDEN_DT)
-    assert relerr(sp.GetSolutionColumn(), g["u_rk3"]) < 1e-11
+    assert relerr(sp.GetSolutionColumn(), g["u_rk3"]) < 1e-12
     assert relerr(sp.ctx.cell_viscosity(), g["nu_rk3"]) < 1e-9
 
 
@@ -327,5 +327,5 @@ def test_energy_based_viscosity_two_parts_with_halo_buffers():
             sp.ctx.rk_stage_inter(stage)
         refresh()
     for sp, p in zip(S, P):
-        assert relerr(sp.GetSolutionColumn().reshape(-1, 135), u3.reshape(-1, 135)[p.local_global]) < 1e-11
+        assert relerr(sp.GetSolutionColumn().reshape(-1, 135), u3.reshape(-1, 135)[p.local_global]) < 1e-12
         assert relerr(sp.ctx.cell_viscosity(), nu3[p.local_global]) < 1e-9

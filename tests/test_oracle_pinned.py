@@ -367,3 +367,48 @@ def test_c_oracle_fr_general_matches_reference(degree, c_next):
         lob = oc.Oracle(m, degree, 0, 2)
         cases.apply_bcs_oracle(lob)
         assert relerr(lob.residual(u, 0.2), ref) < 1e-13
+
+
+def test_reference_drift_under_one_ulp_perturbation():
+    """How far the REFERENCE's own answer moves when every input coefficient is changed by at most one unit in the last
+    place, at the step counts of the many-step GPU parity tests — the yardstick for their tolerance: 1e-12, two orders
+    above these drifts (6e-16 after ten RK3 steps of a smooth state, 1e-14 after eight steps of the double-Mach
+    problem with the WENO limiter; 7e-13 for Sod at degree 3 with the limiter, the one test that keeps 1e-11)."""
+    if not refapi.available(2):
+        pytest.skip("oracle/_ref not built")
+    from minicfd_b200.part import cell_points
+    rng = np.random.default_rng(1)
+
+    def one_ulp(u):
+        return u * (1 + rng.integers(-1, 2, size=u.shape) * 2.0 ** -52)
+
+    for degree in (2, 3):
+        if not refapi.available(degree):
+            continue
+        m = meshmod.box(6, 4, 3, hi=(3.0, 2.0, 1.5), warp=0.1, seed=4)
+        u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), seed=5, amp=1e-4)
+        end = []
+        for start in (u, one_ulp(u)):
+            r = refapi.Ref(m, degree=degree, scheme=refapi.FR, riemann=1)
+            cases.apply_bcs_ref(r, {t: cases.WALL for t in range(6)})
+            r.set_solution(start)
+            t = 0.0
+            for _ in range(10):
+                dt = r.time_step(4e-3, 3)
+                r.rk_update(3, t, dt, 1)
+                t += dt
+            end.append(r.get_solution())
+        assert relerr(end[1], end[0]) < 1e-14
+    import test_gpu_cpp_shim as shim
+    a = shim._double_mach_reference(8, 5)
+    b = shim._double_mach_reference(8, 5, perturb=one_ulp)
+    assert relerr(b, a) < 1e-13
+    # the one case that keeps 1e-11: Sod at degree 3 with weno::Lazy, six steps — the limiter's weights 1 / (beta + 1e-6)^2
+    # on piecewise-constant data carry rounding noise forward: 7e-13 in the reference itself, 1000 x the unlimited run
+    if refapi.available(3):
+        a = shim._sod_reference(1, 6, limiter=True, degree=3)
+        b = shim._sod_reference(1, 6, limiter=True, degree=3, perturb=one_ulp)
+        assert 1e-14 < relerr(b, a) < 1e-11
+        a = shim._sod_reference(1, 4, limiter=False, degree=3)
+        b = shim._sod_reference(1, 4, limiter=False, degree=3, perturb=one_ulp)
+        assert relerr(b, a) < 1e-14
