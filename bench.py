@@ -66,6 +66,8 @@ def parse():
     ap.add_argument("--halo", default="peer", choices=["peer", "nccl"],
                     help="N > 1: ghost exchange by stores into the neighbours' memory (mcfd_peer_*, the default for the "
                          "inviscid nodal schemes) or pack -> NCCL send/recv -> unpack issued from Python")
+    ap.add_argument("--warp", type=float, default=0.0,
+                    help="displace the interior mesh nodes by this fraction of h (non-affine cells: the general metric path)")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of replaying a CUDA graph")
     return ap.parse_args()
 
@@ -223,7 +225,8 @@ def config_dict(args, n_gpus, dims, part):
                         ("weno::Lazy limiter after every stage, " if args.limiter else "") +
                         ("EnergyBasedViscosity updated after every stage, " if args.energy_viscosity else "") +
                         
-                        f"{SCHEME_NAME[args.scheme]} p={args.degree}, {args.riemann.upper()}, RK3, periodic",
+                        f"{SCHEME_NAME[args.scheme]} p={args.degree}, {args.riemann.upper()}, RK3, periodic" +
+                        (f", interior nodes displaced by {args.warp} h" if getattr(args, "warp", 0.0) else ""),
             "cells_per_gpu": args.cells ** 3, "dof_per_gpu": args.cells ** 3 * 5 * (args.degree + 1) ** 3,
             "step": "GetTimeStep + RungeKutta<3>::Update (3 stages)", "parallelism": f"domain decomposition {part}",
             "l2_policy": "state (3 x 80 MB per GPU) exceeds the 126 MB L2; no flush needed"}
@@ -278,7 +281,7 @@ def ours(args):
     px, py, pz = meshmod.factor3(world)
     n = args.cells
     dims = (n * px, n * py, n * pz)
-    m = meshmod.box(*dims, hi=(10.0 * px, 10.0 * py, 10.0 * pz), periodic=True)
+    m = meshmod.box(*dims, hi=(10.0 * px, 10.0 * py, 10.0 * pz), periodic=True, warp=args.warp, seed=7)
     parts = meshmod.block_partition(m, px, py, pz) if world > 1 else None
     part = Part(m, parts, rank, world)
     scheme = {"fr": capi.FR_LOBATTO, "dg": capi.DG_LOBATTO, "dgm": capi.DG_GENERAL}[args.scheme]
@@ -487,6 +490,10 @@ def ours(args):
             line["e2e"] = e2e
         if args.frame_output:
             line["frame_output"] = frame_output(sp, args)
+        if world == 1 and args.warp == 0.0 and not args.no_e2e and args.scheme != "dgm" and args.viscous is None:
+            # the box's cells are parallelepipeds and take the kernel instantiation with one metric per cell; the same
+            # workload on a warped copy of the mesh (general trilinear metric at every node and face point) beside it
+            line["warped_mesh"] = warped_mesh_run(args)
         if world == 1 and not args.no_cpu_baseline:
             res = cpu_run(args, steps=3, warmup=1)
             line["cpu_baseline"] = {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")}
@@ -496,6 +503,41 @@ def ours(args):
         torch.cuda.synchronize()
         dist.barrier()
         dist.destroy_process_group()
+
+
+def warped_mesh_run(args, steps=30, warp=0.15):
+    import torch
+    from minicfd_b200 import capi, fields, mesh as meshmod
+    from minicfd_b200.part import Part
+    from minicfd_b200.spatial import RungeKutta, Spatial, time_step_device
+    n = args.cells
+    m = meshmod.box(n, n, n, hi=(10.0, 10.0, 10.0), periodic=True, warp=warp, seed=7)
+    scheme = {"fr": capi.FR_LOBATTO, "dg": capi.DG_LOBATTO}[args.scheme]
+    sp = Spatial(Part(m), scheme=scheme, degree=args.degree, riemann=RIEMANN[args.riemann], device=torch.cuda.current_device())
+    sp.ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+    sp.Approximate(lambda x: fields.vortex()(x, 0.0))
+    rk = RungeKutta(3)
+    dt_dev = torch.zeros(1, dtype=torch.float64, device="cuda")
+
+    def step():
+        time_step_device(sp, 1.0, 3, dt_dev)
+        rk.UpdateDevice(sp, 0.0, dt_dev.data_ptr())
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    sp.ctx.enable_kernel_timing(True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    kernel_ms, launches = sp.ctx.kernel_time(reset=True)
+    ms = e0.elapsed_time(e1) / steps
+    n_dof = sp.part.n_local * sp.kfields
+    return {"what": f"the same workload on a mesh whose interior nodes are displaced by {warp} h (no cell is a parallelepiped), "
+                    f"{steps} host-launched steps", "ms_per_step": ms, "value": 3.0 * n_dof / (ms * 1e-3),
+            "kernel_ms_per_stage": kernel_ms / max(launches, 1), "finite": bool(np.isfinite(sp.GetSolutionColumn()).all())}
 
 
 def conserved_sums(sp, part, args, world):

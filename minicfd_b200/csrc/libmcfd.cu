@@ -192,10 +192,10 @@ cudaError_t LaunchStageG(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
 }
 
 // The node-line kernel (stage_lines.cuh): inviscid fr::Lobatto / dg::Lobatto.  Its tables are a kernel parameter.
-template <int Q, int R, int CPB>
-cudaError_t LaunchLineR(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
+template <int Q, int R, int CPB, bool kAffine>
+cudaError_t LaunchLineA(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
   using S = LineShape<Q, CPB>;
-  auto kernel = LineStageKernel<Q, R, CPB>;
+  auto kernel = LineStageKernel<Q, R, CPB, kAffine>;
   static DeviceFlags configured;
   if (!configured.Here()) {
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::kSharedBytes);
@@ -207,6 +207,11 @@ cudaError_t LaunchLineR(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
   }
   kernel<<<n_blocks, S::kThreads, S::kSharedBytes, ctx->stream>>>(a, ctx->line_tables);
   return cudaGetLastError();
+}
+// a mesh of parallelepipeds only (uniform and sheared boxes) takes the instantiation with the metric per cell
+template <int Q, int R, int CPB>
+cudaError_t LaunchLineR(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
+  return ctx->mesh.all_affine ? LaunchLineA<Q, R, CPB, true>(ctx, a, n_blocks) : LaunchLineA<Q, R, CPB, false>(ctx, a, n_blocks);
 }
 template <int Q, int CPB>
 cudaError_t LaunchLine(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
@@ -363,7 +368,7 @@ int LaunchStage(mcfd_ctx *ctx, const double *u_in, const double *u0, double *u_o
     e = (ctx->q == 3) ? LaunchStageViscous<3, kP2ViscousCells, kP2ViscousWarps>(ctx, a, n_blocks)
                       : LaunchStageViscous<4, kP3ViscousCells, kP3ViscousWarps>(ctx, a, n_blocks);
   } else if (ctx->use_lines) {
-    e = (ctx->q == 3) ? LaunchLine<3, kLineP2Cells>(ctx, a, n_blocks) : LaunchLine<4, kLineP3Cells>(ctx, a, n_blocks);
+    e = LaunchLine<3, kLineP2Cells>(ctx, a, n_blocks);   // degree 3 stays on the slot kernel (use_lines)
   } else {
     e = (ctx->q == 3) ? LaunchStageQ<3, kP2Cells, kP2Warps>(ctx, a, n_blocks)
                       : LaunchStageQ<4, kP3Cells, kP3Warps>(ctx, a, n_blocks);

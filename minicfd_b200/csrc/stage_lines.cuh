@@ -163,6 +163,20 @@ MCFD_HD PrimA ConsToPrimFlat(const double *c, bool *ok) {
 // normal gives the negated flux up to rounding.  With p >= 0, max(max(p_pvrs, 0) - p_K, 0) = max(p_pvrs - p_K, 0), and
 // q_K = sqrt(1 + (gamma+1)/(2 gamma) max(p_pvrs - p_K, 0) / p_K) takes one reciprocal of p_L p_R for both sides.
 MCFD_HD void HllcFlux(const PrimA &L, const PrimA &R, double nx, double ny, double nz, double *flux) {
+#ifdef MCFD_EXPERIMENT_CHEAP_FLUX   // timing experiment only: how much of the stage is the solver itself
+  {   // central flux 0.5 (F(L) + F(R)) . n: about a quarter of the solver's arithmetic, stable for the few steps timed
+    const double ul = L.u * nx + L.v * ny + L.w * nz, ur = R.u * nx + R.v * ny + R.w * nz;
+    const double ml = L.rho * ul, mr = R.rho * ur, pm = 0.5 * (L.p + R.p);
+    const double el = L.p * kOneOverGm1 + 0.5 * L.rho * (L.u * L.u + L.v * L.v + L.w * L.w);
+    const double er = R.p * kOneOverGm1 + 0.5 * R.rho * (R.u * R.u + R.v * R.v + R.w * R.w);
+    flux[0] = 0.5 * (ml + mr);
+    flux[1] = 0.5 * (ml * L.u + mr * R.u) + pm * nx;
+    flux[2] = 0.5 * (ml * L.v + mr * R.v) + pm * ny;
+    flux[3] = 0.5 * (ml * L.w + mr * R.w) + pm * nz;
+    flux[4] = 0.5 * ((el + L.p) * ul + (er + R.p) * ur);
+    return;
+  }
+#endif
   const double unl = L.u * nx + L.v * ny + L.w * nz;
   const double unr = R.u * nx + R.v * ny + R.w * nz;
   const double rho_avg = (L.rho + R.rho) * 0.5, a_avg = (L.a + R.a) * 0.5;
@@ -219,7 +233,9 @@ struct LineShape {
   static constexpr int kNodeDoubles = 21;
   static constexpr int kStageDoubles = 6 * FQ * 5 * CPB;   // neighbour states at the face points
   static constexpr int kNodeQBytes = (N * 3 + 3) / 4 * 4;
-  static constexpr size_t kSharedBytes = (size_t)(N * kNodeDoubles * CPB + kStageDoubles + kGeomRows * CPB) * sizeof(double)
+  // affine cells (parallelepipeds): per cell and direction the column of J* (3), 1 / its length, its length; det J
+  static constexpr int kAffineRows = 16;
+  static constexpr size_t kSharedBytes = (size_t)(N * kNodeDoubles * CPB + kStageDoubles + (kGeomRows + kAffineRows) * CPB) * sizeof(double)
       + 6 * 8 * FQ + kNodeQBytes + 6 * CPB * (sizeof(int) + 1);
   static_assert(SUB == 1 || SUB == 2 || (SUB == 4 && Q == 4), "lines per warp");
 };
@@ -235,14 +251,15 @@ struct LineThread {
   using S = LineShape<Q, CPB>;
   int lane, warp, lc, sub, block, tile, tl, cell, i, j, cls;
   bool active, valid;
-  double *sF, *sN, *sG;
+  double *sF, *sN, *sG, *sA;
   unsigned char *sNbrNode, *sNodeQ, *sCode;
   int *sNbr;
   MCFD_HD LineThread(const StageArgs &p, const LineTables &tab, int tid, int bid, double *smem) {
     sF = smem;                                                           // [N][21][CPB]
     sN = smem + S::N * S::kNodeDoubles * CPB;                            // [6 FQ][5][CPB]
     sG = sN + S::kStageDoubles;                                          // [21][CPB]
-    sNbrNode = reinterpret_cast<unsigned char *>(sG + kGeomRows * CPB);  // [6][8][FQ]
+    sA = sG + kGeomRows * CPB;                                           // [16][CPB]
+    sNbrNode = reinterpret_cast<unsigned char *>(sA + S::kAffineRows * CPB);   // [6][8][FQ]
     sNodeQ = sNbrNode + 6 * 8 * S::FQ;                                   // [N][3]
     sNbr = reinterpret_cast<int *>(sNodeQ + S::kNodeQBytes);             // [6][CPB]
     sCode = reinterpret_cast<unsigned char *>(sNbr + 6 * CPB);           // [6][CPB]
@@ -299,24 +316,6 @@ MCFD_HD void LineLoad(const StageArgs &p, const LineTables &tab, int tid, int bi
   }
 }
 
-// Everything the CTA shares goes global -> shared asynchronously (no register, no stall at a store): the byte tables
-// (p.line_bytes = nbr_node[6][8][FQ] then node_q[N][3], a device copy of LineTables' members), the geometry rows
-// and the face tables of the block's cells.  LinePrologueWait() + a barrier make them visible.
-template <int Q, int CPB>
-MCFD_HD void LinePrologue(const StageArgs &p, const LineTables &tab, int tid, int bid, double *smem) {
-  using S = LineShape<Q, CPB>;
-  LineThread<Q, CPB> g(p, tab, tid, bid, smem);
-  constexpr int kTableWords = (6 * 8 * S::FQ + S::kNodeQBytes) / 4;
-  for (int x = tid; x < kTableWords; x += S::kThreads) AsyncCopy4(g.sNbrNode + 4 * x, p.line_bytes + 4 * x);
-  const int off = (g.block % S::SUB) * CPB;
-  for (int x = tid; x < kGeomRows * CPB; x += S::kThreads)
-    AsyncCopy8(g.sG + x, p.geom + ((size_t)g.tile * kGeomRows + x / CPB) * kTile + off + x % CPB);
-  for (int x = tid; x < 6 * CPB; x += S::kThreads)
-    AsyncCopy4(g.sNbr + x, p.nbr + ((size_t)g.tile * 6 + x / CPB) * kTile + off + x % CPB);
-  for (int x = tid; x < 6 * CPB / 4; x += S::kThreads)
-    AsyncCopy4(g.sCode + 4 * x, p.code + ((size_t)g.tile * 6 + (4 * x) / CPB) * kTile + off + (4 * x) % CPB);
-}
-
 // The Jacobian rows of the trilinear map along the line (xi_i, eta_j, .): rows 0 and 1 are linear in zeta,
 // row 2 does not depend on it (coordinate/hexahedron.hpp:431-456; the same FMA nesting as ComputeMetric).
 struct LineJacobian {
@@ -334,10 +333,62 @@ MCFD_HD LineJacobian ComputeLineJacobian(const double *g, int gs, double x, doub
   }
   return J;
 }
+// the same for a parallelepiped: r0 = c1, r1 = c2, r2 = c3
+MCFD_HD LineJacobian AffineLineJacobian(const double *g, int gs) {
+  LineJacobian J;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    J.A0[k] = g[(0 + k) * gs]; J.A1[k] = g[(3 + k) * gs]; J.R2[k] = g[(6 + k) * gs];
+    J.B0[k] = 0; J.B1[k] = 0;
+  }
+  return J;
+}
 MCFD_HD void Cross(const double *a, const double *b, double *c) {
   c[0] = a[1] * b[2] - a[2] * b[1];
   c[1] = a[2] * b[0] - a[0] * b[2];
   c[2] = a[0] * b[1] - a[1] * b[0];
+}
+
+// Everything the CTA shares goes global -> shared asynchronously (no register, no stall at a store): the byte tables
+// (p.line_bytes = nbr_node[6][8][FQ] then node_q[N][3], a device copy of LineTables' members), the geometry rows
+// and the face tables of the block's cells.  LinePrologueWait() + a barrier make them visible.
+template <int Q, int CPB, bool kAffine>
+MCFD_HD void LinePrologue(const StageArgs &p, const LineTables &tab, int tid, int bid, double *smem) {
+  using S = LineShape<Q, CPB>;
+  LineThread<Q, CPB> g(p, tab, tid, bid, smem);
+  if (kAffine && tid < CPB) {
+    // Every cell of the mesh is a parallelepiped (c4..c7 = 0): J is constant in the cell.  One thread per cell of the
+    // block takes c1, c2, c3 straight from global memory and leaves the three columns of J*, their lengths and det J
+    // in shared memory — the same operations on the same numbers as the general path performs per node and per face
+    // point, so the results are bit-identical.
+    const double *gm = p.geom + (size_t)g.tile * kGeomRows * kTile + (g.block % S::SUB) * CPB + tid;
+    double c[3][3], nrm[3][3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+#pragma unroll
+      for (int x = 0; x < 3; ++x) c[r][x] = gm[(r * 3 + x) * kTile];
+    }
+    Cross(c[1], c[2], nrm[0]); Cross(c[2], c[0], nrm[1]); Cross(c[0], c[1], nrm[2]);
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      const double n2 = nrm[d][0] * nrm[d][0] + nrm[d][1] * nrm[d][1] + nrm[d][2] * nrm[d][2];
+      const double inv_area = RsqrtC(n2);
+#pragma unroll
+      for (int x = 0; x < 3; ++x) g.sA[(d * 5 + x) * CPB + tid] = nrm[d][x];
+      g.sA[(d * 5 + 3) * CPB + tid] = inv_area;
+      g.sA[(d * 5 + 4) * CPB + tid] = n2 * inv_area;
+    }
+    g.sA[15 * CPB + tid] = c[0][0] * nrm[0][0] + c[0][1] * nrm[0][1] + c[0][2] * nrm[0][2];
+  }
+  constexpr int kTableWords = (6 * 8 * S::FQ + S::kNodeQBytes) / 4;
+  for (int x = tid; x < kTableWords; x += S::kThreads) AsyncCopy4(g.sNbrNode + 4 * x, p.line_bytes + 4 * x);
+  const int off = (g.block % S::SUB) * CPB;
+  for (int x = tid; x < kGeomRows * CPB; x += S::kThreads)
+    AsyncCopy8(g.sG + x, p.geom + ((size_t)g.tile * kGeomRows + x / CPB) * kTile + off + x % CPB);
+  for (int x = tid; x < 6 * CPB; x += S::kThreads)
+    AsyncCopy4(g.sNbr + x, p.nbr + ((size_t)g.tile * 6 + x / CPB) * kTile + off + x % CPB);
+  for (int x = tid; x < 6 * CPB / 4; x += S::kThreads)
+    AsyncCopy4(g.sCode + 4 * x, p.code + ((size_t)g.tile * 6 + (4 * x) / CPB) * kTile + off + (4 * x) % CPB);
 }
 
 // F^_d = F(u) . s for one column s of J* (types.hpp:322-333 with the primitive state q of u; hexahedron.hpp:607-611)
@@ -375,7 +426,7 @@ MCFD_HD void LineStageNeighbour(const StageArgs &p, const LineThread<Q, CPB> &g,
 // thread's later use the finished zeta-direction sum and the primitive state.  The node's own face-flux terms
 // +-coef_F F^_d(own) (fr/general.hpp:305-313, "- F^_h[:, d]") ride on the diagonal of the divergence matrix.
 // The neighbour states of the line's face points are requested first and travel meanwhile.
-template <int Q, int CPB>
+template <int Q, int CPB, bool kAffine>
 MCFD_HD void LinePhaseA(const StageArgs &p, const LineTables &tab, int tid, int bid, double *smem, LineRegs<Q> *t) {
   using S = LineShape<Q, CPB>;
   constexpr int ND = S::kNodeDoubles;
@@ -391,7 +442,8 @@ MCFD_HD void LinePhaseA(const StageArgs &p, const LineTables &tab, int tid, int 
       if (k == 0 || k == Q - 1) LineStageNeighbour<Q, CPB>(p, g, k == 0 ? 0 : 5, g.sNodeQ[(n0 + k) * 3 + 2]);
     }
   }
-  const LineJacobian J = ComputeLineJacobian(g.sG + g.lc, CPB, tab.xi[g.i], tab.xi[g.j]);
+  const LineJacobian J = kAffine ? AffineLineJacobian(g.sG + g.lc, CPB)
+                                 : ComputeLineJacobian(g.sG + g.lc, CPB, tab.xi[g.i], tab.xi[g.j]);
   double *dst = g.sF + (size_t)n0 * ND * CPB + g.lc;
   double f2[Q][5];
 #pragma unroll
@@ -399,7 +451,10 @@ MCFD_HD void LinePhaseA(const StageArgs &p, const LineTables &tab, int tid, int 
     const double z = tab.xi[k];
     double r0[3], r1[3], s[3];
 #pragma unroll
-    for (int x = 0; x < 3; ++x) { r0[x] = fma(z, J.B0[x], J.A0[x]); r1[x] = fma(z, J.B1[x], J.A1[x]); }
+    for (int x = 0; x < 3; ++x) {   // (affine: the same rows at every node, the products below are computed once)
+      r0[x] = kAffine ? J.A0[x] : fma(z, J.B0[x], J.A0[x]);
+      r1[x] = kAffine ? J.A1[x] : fma(z, J.B1[x], J.A1[x]);
+    }
     bool ok;
     PrimA q = ConsToPrimFlat(t->u[k], &ok);       // branch-free: the Q nodes of the line are Q independent streams
     if (!ok) q = ConsToPrimA(t->u[k]);             // clipped or vacuum state
@@ -499,12 +554,22 @@ struct PointSetup {
   bool pad;
   double nr[3], ox, oy, oz, area;
 };
-template <int Q, int CPB>
+template <int Q, int CPB, bool kAffine>
 MCFD_HD PointSetup LinePointSetup(const LineTables &tab, const LineThread<Q, CPB> &g, const LineJacobian &J, int desc) {
   PointSetup s;
   s.k = desc & 3;
   const int dd = (desc >> 2) & 3;
   s.pad = (desc & 16) != 0;
+  if (kAffine) {   // the cell's column dd of J*, its length and the reciprocal are waiting in shared memory
+    const double *a = g.sA + dd * 5 * CPB + g.lc;
+    s.f = dd == 0 ? (g.i == 0 ? 4 : 2) : (dd == 1 ? (g.j == 0 ? 1 : 3) : (s.k == 0 ? 0 : 5));
+    s.q = g.sNodeQ[(((g.i * Q + g.j) * Q) + s.k) * 3 + dd];
+    s.nr[0] = a[0]; s.nr[1] = a[CPB]; s.nr[2] = a[2 * CPB];
+    const double os_ = ((s.f == 2 || s.f == 3 || s.f == 5) ? 1.0 : -1.0) * a[3 * CPB];
+    s.area = a[4 * CPB];
+    s.ox = os_ * s.nr[0]; s.oy = os_ * s.nr[1]; s.oz = os_ * s.nr[2];
+    return s;
+  }
   const double z = tab.xi[s.k];
   double r0[3], r1[3];
 #pragma unroll
@@ -524,7 +589,7 @@ MCFD_HD PointSetup LinePointSetup(const LineTables &tab, const LineThread<Q, CPB
 
 // ---- phase F: the face points of the line, two at a time.  Touches only what this thread wrote in phase A and
 // its own staged neighbour states, so no barrier separates the two.
-template <int Q, int kRiemann, int CPB>
+template <int Q, int kRiemann, int CPB, bool kAffine>
 MCFD_HD void LinePhaseF(const StageArgs &p, const LineTables &tab, int tid, int bid, double *smem) {
   using S = LineShape<Q, CPB>;
   constexpr int FQ = S::FQ, ND = S::kNodeDoubles;
@@ -533,14 +598,15 @@ MCFD_HD void LinePhaseF(const StageArgs &p, const LineTables &tab, int tid, int 
   const int i = g.i, j = g.j, lc = g.lc;
   const int n0 = (i * Q + j) * Q;
   double *own = g.sF + (size_t)n0 * ND * CPB + lc;       // this line's nodes
-  const LineJacobian J = ComputeLineJacobian(g.sG + lc, CPB, tab.xi[i], tab.xi[j]);
+  LineJacobian J;
+  if (!kAffine) J = ComputeLineJacobian(g.sG + lc, CPB, tab.xi[i], tab.xi[j]);
   // Each pass solves two of them in straight-line code — two independent dependency chains per
   // warp — and adds the lifted terms to the accumulators of their nodes in shared memory.
   const int n_pairs = tab.cls_pairs[g.cls];
 #pragma unroll 1
   for (int t = 0; t < n_pairs; ++t) {
-    const PointSetup sa = LinePointSetup<Q, CPB>(tab, g, J, tab.cls_pts[g.cls][2 * t]);
-    const PointSetup sb = LinePointSetup<Q, CPB>(tab, g, J, tab.cls_pts[g.cls][2 * t + 1]);
+    const PointSetup sa = LinePointSetup<Q, CPB, kAffine>(tab, g, J, tab.cls_pts[g.cls][2 * t]);
+    const PointSetup sb = LinePointSetup<Q, CPB, kAffine>(tab, g, J, tab.cls_pts[g.cls][2 * t + 1]);
     double fa[5], fb[5], sca, scb;
     if (kRiemann == kHllc) {
       const double *la = own + (sa.k * ND + 15) * CPB, *lb = own + (sb.k * ND + 15) * CPB;
@@ -603,7 +669,7 @@ MCFD_HD void LineLoadUpdate(const StageArgs &p, const LineTables &tab, int tid, 
     }
   }
 }
-template <int Q, int CPB>
+template <int Q, int CPB, bool kAffine>
 MCFD_HD void LinePhaseN(const StageArgs &p, const LineTables &tab, int tid, int bid, double *smem, const LineUpdateLoads<Q, CPB> &ld) {
   using S = LineShape<Q, CPB>;
   constexpr int FQ = S::FQ, ND = S::kNodeDoubles;
@@ -613,7 +679,8 @@ MCFD_HD void LinePhaseN(const StageArgs &p, const LineTables &tab, int tid, int 
   const bool i_end = i == 0 || i == Q - 1, j_end = j == 0 || j == Q - 1;
   const int n0 = (i * Q + j) * Q;
   const double *own = g.sF + (size_t)n0 * ND * CPB + lc;
-  const LineJacobian J = ComputeLineJacobian(g.sG + lc, CPB, tab.xi[i], tab.xi[j]);
+  LineJacobian J;
+  if (!kAffine) J = ComputeLineJacobian(g.sG + lc, CPB, tab.xi[i], tab.xi[j]);
   const double cF = tab.coef_F;
   double a0[Q], a1[Q], out[Q][5];
 #pragma unroll
@@ -644,12 +711,17 @@ MCFD_HD void LinePhaseN(const StageArgs &p, const LineTables &tab, int tid, int 
         r[c] = fma(a1[m], s1[((m * Q + k) * ND + c) * CPB], r[c]);
       }
     }
-    const double z = tab.xi[k];
-    double r0[3], r1[3], nr[3];
+    double det;
+    if (kAffine) {
+      det = g.sA[15 * CPB + lc];
+    } else {
+      const double z = tab.xi[k];
+      double r0[3], r1[3], nr[3];
 #pragma unroll
-    for (int x = 0; x < 3; ++x) { r0[x] = fma(z, J.B0[x], J.A0[x]); r1[x] = fma(z, J.B1[x], J.A1[x]); }
-    Cross(r1, J.R2, nr);
-    const double det = r0[0] * nr[0] + r0[1] * nr[1] + r0[2] * nr[2];
+      for (int x = 0; x < 3; ++x) { r0[x] = fma(z, J.B0[x], J.A0[x]); r1[x] = fma(z, J.B1[x], J.A1[x]); }
+      Cross(r1, J.R2, nr);
+      det = r0[0] * nr[0] + r0[1] * nr[1] + r0[2] * nr[2];
+    }
     const double inv_det = RcpC(det);
 #pragma unroll
     for (int c = 0; c < 5; ++c) {
@@ -678,7 +750,7 @@ MCFD_HD void LinePhaseN(const StageArgs &p, const LineTables &tab, int tid, int 
 }
 
 #ifdef __CUDACC__
-template <int Q, int kRiemann, int CPB>
+template <int Q, int kRiemann, int CPB, bool kAffine>
 __global__ void __maxnreg__((LineShape<Q, CPB>::kMaxRegs))
 LineStageKernel(const __grid_constant__ StageArgs p, const __grid_constant__ LineTables tab) {
   extern __shared__ double smem[];
@@ -691,32 +763,32 @@ LineStageKernel(const __grid_constant__ StageArgs p, const __grid_constant__ Lin
   }
   LineRegs<Q> t;
   LineLoad<Q, CPB>(p, tab, tid, bid, smem, &t);
-  LinePrologue<Q, CPB>(p, tab, tid, bid, smem);
+  LinePrologue<Q, CPB, kAffine>(p, tab, tid, bid, smem);
   AsyncCopyWait();
   __syncthreads();
-  LinePhaseA<Q, CPB>(p, tab, tid, bid, smem, &t);
-  LinePhaseF<Q, kRiemann, CPB>(p, tab, tid, bid, smem);
+  LinePhaseA<Q, CPB, kAffine>(p, tab, tid, bid, smem, &t);
+  LinePhaseF<Q, kRiemann, CPB, kAffine>(p, tab, tid, bid, smem);
   LineUpdateLoads<Q, CPB> ld;
   LineLoadUpdate<Q, CPB>(p, tab, tid, bid, smem, &ld);    // in flight across the barrier
   __syncthreads();
-  LinePhaseN<Q, CPB>(p, tab, tid, bid, smem, ld);
+  LinePhaseN<Q, CPB, kAffine>(p, tab, tid, bid, smem, ld);
 }
 #else
-template <int Q, int kRiemann, int CPB>
+template <int Q, int kRiemann, int CPB, bool kAffine>
 void RunLineStageBlockOnHost(const StageArgs &p, const LineTables &tab, int bid, double *smem) {
   constexpr int T = LineShape<Q, CPB>::kThreads;
   static LineRegs<Q> regs[T];
   for (int t = 0; t < T; ++t) {
     LineLoad<Q, CPB>(p, tab, t, bid, smem, &regs[t]);
-    LinePrologue<Q, CPB>(p, tab, t, bid, smem);
+    LinePrologue<Q, CPB, kAffine>(p, tab, t, bid, smem);
   }
   static LineUpdateLoads<Q, CPB> ld[T];
   for (int t = 0; t < T; ++t) {
-    LinePhaseA<Q, CPB>(p, tab, t, bid, smem, &regs[t]);
-    LinePhaseF<Q, kRiemann, CPB>(p, tab, t, bid, smem);
+    LinePhaseA<Q, CPB, kAffine>(p, tab, t, bid, smem, &regs[t]);
+    LinePhaseF<Q, kRiemann, CPB, kAffine>(p, tab, t, bid, smem);
     LineLoadUpdate<Q, CPB>(p, tab, t, bid, smem, &ld[t]);
   }
-  for (int t = 0; t < T; ++t) LinePhaseN<Q, CPB>(p, tab, t, bid, smem, ld[t]);
+  for (int t = 0; t < T; ++t) LinePhaseN<Q, CPB, kAffine>(p, tab, t, bid, smem, ld[t]);
 }
 #endif
 

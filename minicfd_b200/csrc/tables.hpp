@@ -261,6 +261,7 @@ struct HostMesh {
   std::vector<double> frames;        // [cell][6][9] normal frame (normal, tangent, bitangent) of that face at its
                                      // quadrature point 0, as rotated::Euler::Rotate receives it (fem.hpp:103-106)
   std::vector<double> length, volume;  // local cells
+  bool all_affine = false;             // every local cell is a parallelepiped: c4..c7 = 0 exactly, J constant per cell
   // optional: the cells' ids in the whole mesh.  The reference decides holder / sharer of a face between two
   // local cells by those (holder = smaller id, mesh/shuffler.hpp:417-420), not by the part-local numbering.
   std::vector<int64_t> global_ids;
@@ -514,6 +515,7 @@ struct HostMesh {
     LobattoRule(q, x, w);
     coef.assign(nc * kGeomRows, 0.0);
     c0.assign(nc * 3, 0.0);
+    all_affine = true;
     length.resize(nl);
     volume.resize(nl);
     static const int kTerm[7][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}, {1, 1, 0}, {0, 1, 1}, {1, 0, 1}, {1, 1, 1}};
@@ -535,6 +537,7 @@ struct HostMesh {
         }
       }
       if (c >= nl) continue;
+      for (int k = 9; k < kGeomRows; ++k) if (coef[c * kGeomRows + k] != 0.0) all_affine = false;
       double vol = 0;
       for (int i = 0; i < q; ++i) for (int j = 0; j < q; ++j) for (int k = 0; k < q; ++k) {
         double r[3][3];

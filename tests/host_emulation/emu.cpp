@@ -29,9 +29,8 @@ void RunStage(StageArgs a, int n_blocks) {
   }
 }
 
-// the node-line kernel of the lumped inviscid schemes (stage_lines.cuh), block by block
-template <int Q, int CPB>
-void RunLineStage(int riemann, StageArgs a, int64_t n_local) {
+template <int Q, int CPB, bool kAffine>
+void RunLineStageA(int riemann, StageArgs a, int64_t n_local) {
   using S = LineShape<Q, CPB>;
   std::vector<double> smem(S::kSharedBytes / sizeof(double) + 1);
   const LineTables tab = MakeLineTables(c_tab, Q, kTile / CPB);
@@ -39,10 +38,17 @@ void RunLineStage(int riemann, StageArgs a, int64_t n_local) {
   a.line_bytes = bytes.data();
   const int n_blocks = (int)((n_local + CPB - 1) / CPB);
   for (int b = 0; b < n_blocks; ++b) {
-    if (riemann == 0) RunLineStageBlockOnHost<Q, kExact, CPB>(a, tab, b, smem.data());
-    else if (riemann == 1) RunLineStageBlockOnHost<Q, kHllc, CPB>(a, tab, b, smem.data());
-    else RunLineStageBlockOnHost<Q, kAusm, CPB>(a, tab, b, smem.data());
+    if (riemann == 0) RunLineStageBlockOnHost<Q, kExact, CPB, kAffine>(a, tab, b, smem.data());
+    else if (riemann == 1) RunLineStageBlockOnHost<Q, kHllc, CPB, kAffine>(a, tab, b, smem.data());
+    else RunLineStageBlockOnHost<Q, kAusm, CPB, kAffine>(a, tab, b, smem.data());
   }
+}
+// the node-line kernel of the lumped inviscid schemes (stage_lines.cuh), block by block; the affine instantiation
+// when every local cell is a parallelepiped, as the library chooses
+template <int Q, int CPB>
+void RunLineStage(int riemann, StageArgs a, int64_t n_local, bool affine) {
+  if (affine) RunLineStageA<Q, CPB, true>(riemann, a, n_local);
+  else RunLineStageA<Q, CPB, false>(riemann, a, n_local);
 }
 
 template <int Q, int CPB, int NW>
@@ -126,11 +132,11 @@ int emu_stage(int degree, int scheme, int riemann, int64_t n_nodes, const double
   }
   int n_blocks = (int)((n_local + cpb - 1) / cpb);
   const bool lines = !viscous && scheme != 2 && line_cells != 0;   // what LaunchStage of the library picks
-  if (lines && q == 3 && line_cells == 16) RunLineStage<3, 16>(riemann, a, n_local);
-  else if (lines && q == 3) RunLineStage<3, 32>(riemann, a, n_local);
-  else if (lines && line_cells == 32) RunLineStage<4, 32>(riemann, a, n_local);
-  else if (lines && line_cells == 8) RunLineStage<4, 8>(riemann, a, n_local);
-  else if (lines) RunLineStage<4, 16>(riemann, a, n_local);
+  if (lines && q == 3 && line_cells == 16) RunLineStage<3, 16>(riemann, a, n_local, mesh.all_affine);
+  else if (lines && q == 3) RunLineStage<3, 32>(riemann, a, n_local, mesh.all_affine);
+  else if (lines && line_cells == 32) RunLineStage<4, 32>(riemann, a, n_local, mesh.all_affine);
+  else if (lines && line_cells == 8) RunLineStage<4, 8>(riemann, a, n_local, mesh.all_affine);
+  else if (lines) RunLineStage<4, 16>(riemann, a, n_local, mesh.all_affine);
   else if (q == 3) RunStageQ<3, kP2Cells, kP2Warps>(riemann, a, n_blocks);
   else RunStageQ<4, kP3Cells, kP3Warps>(riemann, a, n_blocks);
   for (int64_t c = 0; c < n_local; ++c)
