@@ -39,6 +39,22 @@ SCHEME_NAME = {"fr": "FR-Lobatto", "dg": "DG-Lobatto", "dgm": "dg::General (moda
 RIEMANN = {"exact": 0, "hllc": 1, "ausm": 2}
 
 
+def stage_kernel_name(args):
+    """The kernel behind a stage of this configuration (libmcfd.cu: mcfd_create's use_lines / LaunchStage)."""
+    q = args.degree + 1
+    if args.scheme == "dgm":
+        return f"mcfd::DgmStageKernel (degree {args.degree})"
+    if args.viscous is None and not args.energy_viscosity and q == 3:
+        return f"mcfd::LineStageKernel<{q}, {args.riemann}, 16 cells per CTA>"
+    return f"mcfd::StageKernel<{q}, {args.riemann}>"
+
+
+def traffic_shape(args, world):
+    """Key of profiles/stage_kernel_traffic.json: the configuration whose stage kernel the ncu capture profiled."""
+    plain = args.viscous is None and not args.limiter and not args.energy_viscosity and args.warp == 0.0
+    return f"{args.scheme} p{args.degree} {args.riemann} {args.cells}^3 cells per GPU {'inviscid' if plain else 'other'} n{world}"
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -63,8 +79,10 @@ def parse():
                          "cell's VTK hexahedron, copied to the host), next to the reference's vtk::Writer::Prepare on the CPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-features", action="store_true",
+                    help="skip the short runs of the other configurations (viscous, limiter, ..., BASELINE config 5)")
     ap.add_argument("--halo", default="peer", choices=["peer", "nccl"],
-                    help="N > 1: ghost exchange by stores into the neighbours' memory (mcfd_peer_*, the default for the "
+                    help="N > 1: ghost exchange by device-to-device copies into the neighbours' memory (mcfd_peer_*, the default for the "
                          "inviscid nodal schemes) or pack -> NCCL send/recv -> unpack issued from Python")
     ap.add_argument("--warp", type=float, default=0.0,
                     help="displace the interior mesh nodes by this fraction of h (non-affine cells: the general metric path)")
@@ -217,8 +235,19 @@ def metric_name(args):
     return f"DOF-updates/s per RK stage (p={args.degree} {what}, hexa)"
 
 
+def l2_policy(args):
+    dof = algorithmic_bytes(args)[2]
+    mb = 3 * args.cells ** 3 * dof * 8 / 1e6
+    if mb > 126.0:
+        return f"state (3 x {mb / 3:.0f} MB per GPU) exceeds the 126 MB L2; no flush needed"
+    return (f"state (3 x {mb / 3:.0f} MB per GPU) FITS in the 126 MB L2 and nothing is flushed between steps: "
+            "an L2-assisted number")
+
+
 def config_dict(args, n_gpus, dims, part):
-    return {"workload": f"BASELINE config 2: synthetic structured box, {dims[0]}x{dims[1]}x{dims[2]} Hexahedron8 "
+    label = ("BASELINE config 2" if (args.degree, args.cells) == (2, 42) else
+             "BASELINE config 5" if (args.degree, args.cells) == (3, 32) else "other size")
+    return {"workload": f"{label}: synthetic structured box, {dims[0]}x{dims[1]}x{dims[2]} Hexahedron8 "
                         f"cells total ({args.cells}^3 per GPU), "
                         + ("Euler isentropic vortex, " if args.viscous is None else
                            f"Navier-Stokes (nu={args.viscous}, direct-DG face flux) on the isentropic vortex, ") +
@@ -229,7 +258,7 @@ def config_dict(args, n_gpus, dims, part):
                         (f", interior nodes displaced by {args.warp} h" if getattr(args, "warp", 0.0) else ""),
             "cells_per_gpu": args.cells ** 3, "dof_per_gpu": args.cells ** 3 * 5 * (args.degree + 1) ** 3,
             "step": "GetTimeStep + RungeKutta<3>::Update (3 stages)", "parallelism": f"domain decomposition {part}",
-            "l2_policy": "state (3 x 80 MB per GPU) exceeds the 126 MB L2; no flush needed"}
+            "l2_policy": l2_policy(args)}
 
 
 def reference_arm(args):
@@ -261,12 +290,51 @@ def reference_arm(args):
 # ---------------------------------------------------------------------------------------------------
 # our arm
 # ---------------------------------------------------------------------------------------------------
+def algorithmic_bytes(args):
+    """Algorithmic HBM bytes per DOF-update of one RK stage (+ what follows every stage) of a configuration, and
+    how the figure is made up (DESIGN.md section 4).  DOFs per cell: 5 N for the nodal schemes, 5 M for dg::General."""
+    n = (args.degree + 1) ** 3
+    dof = 5 * n if args.scheme != "dgm" else 5 * (10 if args.degree == 2 else 20)
+    m = 10 if args.degree == 2 else 20
+    state = 3 * 8 * dof                       # read the stage's state, read u0, write the next state
+    geom = 192                                # 8 vertices x 3 doubles
+    bas = (3 + m * (m + 1) // 2 + 3) * 8      # centre, lower-triangular orthonormalisation, lengths
+    parts = {"state (read, read u0, write)": state, "vertices": geom}
+    if args.scheme == "dgm":
+        parts["Taylor form written and read once"] = 2 * 8 * dof
+        parts["per-cell basis"] = bas
+    if args.viscous is not None or args.energy_viscosity:
+        # TraceKernel: gradients at every node (15 N) and Hessian.n at every face point (15 x 6 Q^2), written once and
+        # read once.  The neighbours' reads at the face points are second reads of the same bytes (L2) and not counted;
+        # the ncu captures of round 1 show 22 KB of DRAM traffic per cell and stage for 22.7 KB counted here.
+        q2 = (args.degree + 1) ** 2
+        parts["traces (gradients + Hessian.n), written and read once"] = 2 * 8 * (15 * n + 15 * 6 * q2)
+    if args.energy_viscosity:
+        parts["damping matrix + state read by ViscosityKernel"] = 8 * n * n + 8 * dof
+    if args.limiter:
+        # ModalKernel: state -> orthonormal + Taylor coefficients; WenoLazyKernel: own + 6 neighbours' Taylor
+        # coefficients (each cell's read once algorithmically), basis, limited state written
+        parts["limiter: state read, limited state written"] = 2 * 8 * dof
+        parts["limiter: modal + Taylor coefficients written and read once"] = 4 * 8 * 5 * m
+        parts["limiter: per-cell basis, twice"] = 2 * bas
+    total = float(sum(parts.values()))
+    return total / dof, {k: v / dof for k, v in parts.items()}, dof
+
+
+FEATURES = [   # name, overrides of the headline arguments
+    ("viscous", {"viscous": 0.01}),
+    ("limiter", {"limiter": True}),
+    ("energy_viscosity", {"energy_viscosity": True}),
+    ("dgm", {"scheme": "dgm"}),
+    ("config5_p3", {"degree": 3, "cells": 32}),
+]
+
+
 def ours(args):
+    import copy
+    import gc
     import torch
     import torch.distributed as dist
-    from minicfd_b200 import capi, fields, halo, mesh as meshmod
-    from minicfd_b200.part import Part
-    from minicfd_b200.spatial import RungeKutta, Spatial
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -278,6 +346,48 @@ def ours(args):
         # NCCL's kernels must not queue behind the thousands of pending CTAs of the inner-cell kernel
         os.environ.setdefault("TORCH_NCCL_HIGH_PRIORITY", "1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    line = measure(args, world, rank, local_rank)
+    plain = (args.viscous is None and not args.limiter and not args.energy_viscosity and args.scheme == "fr"
+             and args.degree == 2 and args.warp == 0.0)
+    if plain and world == 1 and not args.no_features:
+        # the other configurations of the path, briefly, each with its own algorithmic-bytes roofline.  One GPU only:
+        # under torchrun every one of them is its own run (e.g. `--gpus 8 --degree 3 --cells 32` for BASELINE
+        # config 5), so that the headline line never waits on a second rendezvous
+        feats = {}
+        for name, over in FEATURES:
+            fa = copy.copy(args)
+            for k, v in over.items():
+                setattr(fa, k, v)
+            fa.steps, fa.warmup, fa.no_e2e, fa.no_cpu_baseline, fa.frame_output = 12, 3, True, True, False
+            gc.collect()
+            torch.cuda.empty_cache()
+            try:
+                res = measure(fa, world, rank, local_rank, nested=True)
+            except Exception as e:      # a feature must not take the headline down
+                res = {"error": f"{type(e).__name__}: {e}"}
+            if rank == 0:
+                feats[name] = res if "error" in res else {
+                    "metric": res["metric"], "workload": res["config"]["workload"], "value": res["value"],
+                    "ms_per_step": res["ms_per_step"], "steps": res["steps"], "gpu_launches": res["gpu_launches"],
+                    "cuda_graph": res["config"]["cuda_graph"], "roofline": res["roofline"], "check": res["check"]}
+        if rank == 0:
+            line["features"] = feats
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        torch.cuda.synchronize()
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def measure(args, world, rank, local_rank, nested=False):
+    """One configuration: warm up, time args.steps steps, return the JSON line's dictionary on rank 0."""
+    import torch
+    import torch.distributed as dist
+    from minicfd_b200 import capi, fields, halo, mesh as meshmod
+    from minicfd_b200.part import Part
+    from minicfd_b200.spatial import RungeKutta, Spatial
+
     px, py, pz = meshmod.factor3(world)
     n = args.cells
     dims = (n * px, n * py, n * pz)
@@ -461,19 +571,30 @@ def ours(args):
             peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
         else:
             peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-        b_alg = 24.0 + 192.0 / sp.kfields
+        b_alg, b_parts, _ = algorithmic_bytes(args)
         per_launch_ms = kernel_ms / max(kernel_launches, 1)
         # one launch per stage when there is no ghost layer; with ghosts a stage is two launches
         launches_per_stage = kernel_launches / (3.0 * k_steps)
         achieved = b_alg * n_dof_local / (per_launch_ms * launches_per_stage * 1e-3) / 1e9
+        over = "the stage kernel's launches"
+        if args.viscous is not None or args.energy_viscosity or args.limiter or args.scheme == "dgm":
+            # several kernels per stage (traces, limiter, viscosity, Taylor form): the bytes are those of the whole
+            # stage, so the time is the whole step's
+            achieved = b_alg * 3.0 * n_dof_local / ((ms / args.steps) * 1e-3) / 1e9
+            over = "the whole step (every kernel of the three stages and GetTimeStep)"
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": None, "peak_source": peak_src, "kernel": "mcfd::StageKernel",
-                    "algorithmic_bytes_per_dof_update": b_alg, "kernel_ms_per_stage": per_launch_ms * launches_per_stage,
+                    "traffic": None, "peak_source": peak_src, "kernel": stage_kernel_name(args), "over": over,
+                    "algorithmic_bytes_per_dof_update": b_alg, "algorithmic_bytes_made_of": b_parts,
+                    "kernel_ms_per_stage": per_launch_ms * launches_per_stage,
                     "kernel_share_of_step": (kernel_ms / k_steps) / (ms / args.steps),
                     "kernel_timing": f"CUDA events around each stage launch over {k_steps} host-launched steps"}
+        # DRAM bytes per launch from the committed ncu capture: only for the shape that capture profiled
         traffic_path = os.path.join(ROOT, "profiles", "stage_kernel_traffic.json")
         if os.path.exists(traffic_path):
-            roofline["traffic"] = json.load(open(traffic_path)).get("dram_bytes_per_launch")
+            measured = json.load(open(traffic_path))
+            if measured.get("shape") == traffic_shape(args, world):
+                roofline["traffic"] = measured.get("dram_bytes_per_launch")
+                roofline["traffic_source"] = measured.get("source")
         line = {"metric": metric_name(args), "value": value, "unit": "DOF-updates/s",
                 "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -482,7 +603,8 @@ def ours(args):
                 "clocks": clocks.summary(),
                 "roofline": roofline, "gpu_launches": int(launches),
                 "halo": ("none (one part)" if world == 1 else
-                         "peer stores + epoch words, step enqueued by the library (mcfd_peer_step)" if use_peer else
+                         "stage kernel packs, copy engines deliver into the neighbours' receive stages, epoch words; step "
+                         "enqueued by the library (mcfd_peer_step)" if use_peer else
                          "pack -> NCCL send/recv -> unpack, issued per stage from Python"),
                 "check": conservation_check(sums0, sums1),
                 "host_issue_ms_per_step": host_issue_ms / args.steps}
@@ -497,12 +619,11 @@ def ours(args):
         if world == 1 and not args.no_cpu_baseline:
             res = cpu_run(args, steps=3, warmup=1)
             line["cpu_baseline"] = {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")}
-        print(json.dumps(line))
     if world > 1:
         comm.drain()
         torch.cuda.synchronize()
         dist.barrier()
-        dist.destroy_process_group()
+    return line if rank == 0 else None
 
 
 def warped_mesh_run(args, steps=30, warp=0.15):

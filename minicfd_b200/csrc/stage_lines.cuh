@@ -1,20 +1,34 @@
-// stage_lines.cuh — the inviscid stage kernel of the lumped Lobatto schemes (fr::Lobatto, dg::Lobatto),
+// stage_lines.cuh — the inviscid stage kernel of the lumped Lobatto schemes (fr::Lobatto, dg::Lobatto) at p = 2,
 // "node line" formulation.  Included at the end of kernels.cuh.
 //
 // Same mathematics and the same HBM layout as StageKernel (kernels.cuh), different mapping onto the machine:
-//   * lanes are still the cells of a tile (every global access is a whole 256-byte row);
-//   * a thread owns one LINE of Q nodes (i, j, 0..Q-1) of its cell, k compile time, (i, j) from the warp id, so
-//     every register array index and every shared-memory offset is an immediate — no per-slot node tables,
-//     no n / FQ, n % Q at run time;
-//   * the k-direction of the flux divergence never leaves the registers; only F^_xi and F^_eta (10 of the 15
-//     contravariant flux components per node) cross warps through shared memory, behind ONE barrier;
-//   * every face point is solved by the thread that owns its node: own state and residual stay in registers,
-//     the lifted term is added in place, nothing is parked in shared memory and gathered again;
+//   * lanes are cells of a tile: 16 cells per CTA and two node lines per warp, so a global access is a 128-byte half
+//     row per line;
+//   * a thread owns one LINE of Q nodes (i, j, 0..Q-1) of its cell, k compile time; (i, j) comes from a table indexed
+//     by (warp, lane / 16) whose lines are sorted by CLASS (how many of i, j lie on a face), so a warp never mixes
+//     classes and every branch on "my line has face points in direction xi / eta" is warp uniform;
+//   * phase A: per node the primitive state, the three contravariant fluxes, the zeta part of the divergence (which
+//     never leaves the thread).  Shared memory per node and cell: F^_xi (5), F^_eta (5), the residual accumulator
+//     (5), the primitive state and sound speed (6) — 21 doubles;
+//   * phase F (no barrier between A and F: a thread touches only what it wrote itself): every face point is solved
+//     by the thread that owns its node, two points per pass through a branch-free HLLC (two independent
+//     instruction streams per thread); boundary kinds, clipped states and the other solvers go through one
+//     out-of-line copy per point.  The neighbours' states at the face points were requested in phase A and arrive
+//     in shared memory without passing through registers (LDGSTS), `sN[6 Q^2][5][cells]`;
+//   * ONE barrier, then phase N: the xi and eta parts of the divergence from the other lines' F^, 1/det J, the RK
+//     update, the store — and, when the part has neighbours on other GPUs, the packed copy of a send cell's row
+//     into the send stage (peer.cuh);
 //   * the Jacobian rows of the trilinear map split into a part that is constant along the line and a part
 //     linear in zeta, so the metric of a node costs 6 FMA + 3 cross products, and the face normals of a line
-//     come from the same pieces;
+//     come from the same pieces; a mesh whose cells are all parallelepipeds takes an instantiation with one
+//     metric per cell (kAffine; bit-identical results, measured: no faster — the kernel is latency bound);
 //   * reciprocals and square roots: one MUFU seed + one cubic step; HLLC with the two square roots per side
-//     merged (a_K q_K is one root) and one reciprocal per star region.
+//     merged (a_K q_K is one root) and one reciprocal per star region;
+//   * the per-degree tables travel as a kernel parameter (constant bank), the byte tables are staged in shared
+//     memory by the prologue together with the geometry rows and the face tables of the CTA's cells.
+// Shape at p = 2: 5 warps per CTA, 111 KB of shared memory, 166 registers, two CTAs per SM (the register file is
+// 16 K registers per SM sub-partition; the shared-memory carve-out has to be raised to hold two CTAs).
+// Measured history of this kernel and of the variants that did not pay off: profiles/r2_kernel_history.md.
 // Reference members restated: fr::General::AddFluxDivergence spatial/fr/general.hpp:271-288,
 // fr::Lobatto::AddFluxToHolderAndSharer spatial/fr/lobatto.hpp:232-251, fr::General::GetFluxForHolderAndSharer
 // fr/general.hpp:296-315, dg::Lobatto dg/lobatto.hpp:143-191, boundary loops fr/lobatto.hpp:278-428,
