@@ -3,7 +3,9 @@
 #ifndef DEMO_BOX_MESH_HPP_
 #define DEMO_BOX_MESH_HPP_
 
+#include <algorithm>
 #include <cmath>
+#include <map>
 #include <cstdint>
 #include <string>
 #include <utility>
@@ -41,6 +43,96 @@ void BuildBox(Part *part, std::vector<double> const &xs, std::vector<double> con
     if (k == nz - 1) add(5);
   }
   part->SetMesh(std::move(nodes), std::move(cells), (int64_t)nx * ny * nz, 0, std::move(bfaces), names);
+}
+
+// The same box cut into px x py x pz blocks, this rank's block as a part the way the reference's Part numbers one
+// (part.hpp:746-775): local cells in the order inner (no neighbour in another part), then inter, each by ascending
+// global id; then the ghost cells — the face neighbours owned by other parts — grouped by owner.  Send and receive
+// lists name the same cells in the same order on both sides (ascending global id).  Stand-in for
+// `mesh::Shuffler::PartitionAndShuffle` + `partition/<rank>.txt` (shuffler.hpp:436-506).
+template <class Part, class NameOf>
+void BuildBoxPart(Part *part, std::vector<double> const &xs, std::vector<double> const &ys, std::vector<double> const &zs,
+    NameOf &&name_of, int px, int py, int pz) {
+  const int nx = (int)xs.size() - 1, ny = (int)ys.size() - 1, nz = (int)zs.size() - 1;
+  const int rank = part->mpi_rank();
+  std::vector<double> nodes;
+  for (int k = 0; k <= nz; ++k) for (int j = 0; j <= ny; ++j) for (int i = 0; i <= nx; ++i) {
+    nodes.push_back(xs[i]); nodes.push_back(ys[j]); nodes.push_back(zs[k]);
+  }
+  auto nid = [&](int i, int j, int k) { return (int64_t)i + (nx + 1) * (j + (int64_t)(ny + 1) * k); };
+  auto gid = [&](int i, int j, int k) { return (int64_t)i + nx * (j + (int64_t)ny * k); };
+  auto owner = [&](int i, int j, int k) { return (i * px / nx) + px * ((j * py / ny) + py * (k * pz / nz)); };
+  static const int step[6][3] = {{0, 0, -1}, {0, -1, 0}, {1, 0, 0}, {0, 1, 0}, {-1, 0, 0}, {0, 0, 1}};   // faces 0..5
+  std::vector<int64_t> inner, inter;
+  std::map<int, std::vector<int64_t>> send_to, recv_from;   // by part, ascending global id
+  for (int k = 0; k < nz; ++k) for (int j = 0; j < ny; ++j) for (int i = 0; i < nx; ++i) {
+    if (owner(i, j, k) != rank) continue;
+    bool touches = false;
+    for (int f = 0; f < 6; ++f) {
+      const int a = i + step[f][0], b = j + step[f][1], c = k + step[f][2];
+      if (a < 0 || a >= nx || b < 0 || b >= ny || c < 0 || c >= nz) continue;
+      const int q = owner(a, b, c);
+      if (q == rank) continue;
+      touches = true;
+      auto &s = send_to[q];
+      if (s.empty() || s.back() != gid(i, j, k)) s.push_back(gid(i, j, k));
+      recv_from[q].push_back(gid(a, b, c));
+    }
+    (touches ? inter : inner).push_back(gid(i, j, k));
+  }
+  std::vector<int64_t> order = inner;
+  order.insert(order.end(), inter.begin(), inter.end());
+  const int64_t n_local = (int64_t)order.size();
+  typename Part::Halo halo;
+  for (auto &kv : recv_from) {
+    auto &r = kv.second;
+    std::sort(r.begin(), r.end());
+    r.erase(std::unique(r.begin(), r.end()), r.end());
+    halo.parts.push_back(kv.first);
+    halo.recv_counts.push_back((int64_t)r.size());
+    for (int64_t g : r) { halo.recv_cells.push_back((int64_t)order.size()); order.push_back(g); }
+  }
+  std::map<int64_t, int64_t> local_of;
+  for (int64_t c = 0; c < (int64_t)order.size(); ++c) local_of[order[c]] = c;
+  for (auto &kv : send_to) {   // std::map: the same part order as recv_from (a face neighbour relation is symmetric)
+    std::sort(kv.second.begin(), kv.second.end());
+    halo.send_counts.push_back((int64_t)kv.second.size());
+    for (int64_t g : kv.second) halo.send_cells.push_back(local_of[g]);
+  }
+  std::vector<int64_t> cells, bfaces;
+  std::vector<std::string> names;
+  static const int fn[6][4] = {{0, 3, 2, 1}, {0, 1, 5, 4}, {1, 2, 6, 5}, {2, 3, 7, 6}, {0, 4, 7, 3}, {4, 5, 6, 7}};
+  for (int64_t idx = 0; idx < (int64_t)order.size(); ++idx) {
+    const int64_t g = order[idx];
+    const int i = (int)(g % nx), j = (int)((g / nx) % ny), k = (int)(g / ((int64_t)nx * ny));
+    int64_t c[8] = {nid(i, j, k), nid(i + 1, j, k), nid(i + 1, j + 1, k), nid(i, j + 1, k),
+                    nid(i, j, k + 1), nid(i + 1, j, k + 1), nid(i + 1, j + 1, k + 1), nid(i, j + 1, k + 1)};
+    cells.insert(cells.end(), c, c + 8);
+    if (idx >= n_local) continue;
+    auto add = [&](int f) {
+      for (int m = 0; m < 4; ++m) bfaces.push_back(c[fn[f][m]]);
+      names.push_back(name_of(f, i, j, k));
+    };
+    if (k == 0) add(0);
+    if (j == 0) add(1);
+    if (i == nx - 1) add(2);
+    if (j == ny - 1) add(3);
+    if (i == 0) add(4);
+    if (k == nz - 1) add(5);
+  }
+  std::vector<std::string> sections;   // every section of the box, also those this part has no face of
+  for (int k = 0; k < nz; ++k) for (int j = 0; j < ny; ++j) for (int i = 0; i < nx; ++i) {
+    const bool on[6] = {k == 0, j == 0, i == nx - 1, j == ny - 1, i == 0, k == nz - 1};
+    for (int f = 0; f < 6; ++f) {
+      if (!on[f]) continue;
+      std::string name = name_of(f, i, j, k);
+      if (std::find(sections.begin(), sections.end(), name) == sections.end()) sections.push_back(name);
+    }
+  }
+  part->DeclareSections(sections);
+  part->SetMesh(std::move(nodes), std::move(cells), n_local, (int64_t)order.size() - n_local, std::move(bfaces), names,
+      std::move(halo));
+  part->SetCellGlobalIds(order);
 }
 
 inline std::vector<double> Uniform(double lo, double hi, int n) {

@@ -1,15 +1,22 @@
 // demo/euler/shock_tube.cpp — Sod shock tube (BASELINE.json config 1) written against the same template
 // API the reference's driver uses (demo/euler/sourceless.hpp:15-111, demo/euler/shock_tube.cpp:5-66,
 // demo/euler/sourceless.cpp:107-221), with the GPU path selected by the include directory alone:
-//     g++ -std=c++20 -I include demo/euler/shock_tube.cpp -L minicfd_b200 -lminicfd_b200
+//     g++ -std=c++20 -I include -I include/mini/b200/nompi demo/euler/shock_tube.cpp -L minicfd_b200 -lminicfd_b200
+// (the second -I only where there is no MPI: it maps the driver's handful of MPI calls onto shared memory).
 // Differences from the reference driver: the mesh is a structured box built in memory instead of
-// gmsh -> CGNS -> METIS (out of scope), and there is no JSON / CGNS / VTK I/O.
+// gmsh -> CGNS -> METIS (out of scope), and there is no JSON / CGNS I/O.
+// One process per part, like the reference:  MCFD_SESSION=s MCFD_WORLD_SIZE=2 MCFD_RANK=<r> ./shock_tube ...
+// cuts the box into MCFD_WORLD_SIZE slabs along x; the ghost cells' coefficients travel between the GPUs behind
+// Part::ShareGhostCellCoeffs / UpdateGhostCellCoeffs, the time step through MPI_Allreduce(MIN) as in sourceless.cpp:194.
 // Prints the solution column's L1 norm per component and writes the final column to a binary file.
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <string>
 #include <vector>
+
+#include "mpi.h"
+#include "../box_mesh.hpp"
 
 using Scalar = double;
 constexpr int kDimensions = 3;
@@ -101,37 +108,26 @@ Value MyIC(const Global &xyz) { return xyz[0] < 2.5 ? given_value_left : given_v
 Value GivenLeft(const Global &, double) { return given_value_left; }
 Value GivenRight(const Global &, double) { return given_value_right; }
 
-static void BuildBox(Part *part, int nx, int ny, int nz, double lx, double ly, double lz) {
-  std::vector<double> nodes;
-  for (int k = 0; k <= nz; ++k) for (int j = 0; j <= ny; ++j) for (int i = 0; i <= nx; ++i) {
-    nodes.push_back(lx * i / nx); nodes.push_back(ly * j / ny); nodes.push_back(lz * k / nz);
-  }
-  auto nid = [&](int i, int j, int k) { return (int64_t)i + (nx + 1) * (j + (int64_t)(ny + 1) * k); };
-  std::vector<int64_t> cells, bfaces;
-  std::vector<std::string> names;
-  static const int fn[6][4] = {{0, 3, 2, 1}, {0, 1, 5, 4}, {1, 2, 6, 5}, {2, 3, 7, 6}, {0, 4, 7, 3}, {4, 5, 6, 7}};
-  for (int k = 0; k < nz; ++k) for (int j = 0; j < ny; ++j) for (int i = 0; i < nx; ++i) {
-    int64_t c[8] = {nid(i, j, k), nid(i + 1, j, k), nid(i + 1, j + 1, k), nid(i, j + 1, k),
-                    nid(i, j, k + 1), nid(i + 1, j, k + 1), nid(i + 1, j + 1, k + 1), nid(i, j + 1, k + 1)};
-    cells.insert(cells.end(), c, c + 8);
-    auto add = [&](int f, const char *name) { for (int m = 0; m < 4; ++m) bfaces.push_back(c[fn[f][m]]); names.push_back(name); };
-    if (i == 0) add(4, "Left");
-    if (i == nx - 1) add(2, "Right");
-    if (j == 0) add(1, "Front");
-    if (j == ny - 1) add(3, "Back");
-    if (k == 0) add(0, "Bottom");
-    if (k == nz - 1) add(5, "Top");
-  }
-  part->SetMesh(std::move(nodes), std::move(cells), (int64_t)nx * ny * nz, 0, std::move(bfaces), names);
+static const char *SectionName(int face, int, int, int) {   // input/shock_tube.geo:33-38
+  static const char *names[6] = {"Bottom", "Front", "Right", "Back", "Left", "Top"};
+  return names[face];
 }
 
 int main(int argc, char *argv[]) {
   int n_steps = argc > 1 ? std::atoi(argv[1]) : 20;
   const char *out_name = argc > 2 ? argv[2] : nullptr;
   const char *frame_dir = argc > 3 ? argv[3] : nullptr;   // where Frame0 / Frame<n_steps> go (.pvtu + .vtu)
+  MPI_Init(NULL, NULL);                       // sourceless.cpp:60-66
+  int n_core, i_core;
+  MPI_Comm_size(MPI_COMM_WORLD, &n_core);
+  MPI_Comm_rank(MPI_COMM_WORLD, &i_core);
   // input/shock_tube.geo:4-31: [0,5] x [0,0.2] x [0,0.3], h = 0.1
-  Part part(0, 1);
-  BuildBox(&part, 50, 2, 3, 5.0, 0.2, 0.3);
+  auto part = Part(i_core, n_core);           // sourceless.cpp:107, the mesh handed over in memory
+  {
+    auto xs = demo::Uniform(0, 5.0, 50), ys = demo::Uniform(0, 0.2, 2), zs = demo::Uniform(0, 0.3, 3);
+    if (n_core == 1) demo::BuildBox(&part, xs, ys, zs, SectionName);
+    else demo::BuildBoxPart(&part, xs, ys, zs, SectionName, n_core, 1, 1);
+  }
   part.SetFieldNames({"Density", "MomentumX", "MomentumY", "MomentumZ", "EnergyStagnationDensity"});   // sourceless.cpp:109-110
   if (frame_dir) part.SetDirectoryName(frame_dir);
 #ifdef LIMITER   // demo/euler/sourceless.cpp:114-120
@@ -182,7 +178,9 @@ int main(int argc, char *argv[]) {
   Temporal temporal;
   double t = 0, t_stop = 0.2, dt_max = t_stop / 200;   // sourceless.cpp:68-74 with 10 frames x 20 steps
   for (int i = 0; i < n_steps; ++i) {                  // sourceless.cpp:187-215
-    double dt = spatial.GetTimeStep(dt_max, kOrders);
+    double dt_local = spatial.GetTimeStep(dt_max, kOrders);
+    double dt;  // i.e. dt_global
+    MPI_Allreduce(&dt_local, &dt, 1, MPI_DOUBLE, MPI_MIN, MPI_COMM_WORLD);
     temporal.Update(&spatial, t, dt);
     t += dt;
   }
@@ -198,10 +196,19 @@ int main(int argc, char *argv[]) {
   }
   std::printf("max cell viscosity %.15e\n", nu_max);
 #endif
-  if (out_name) {
+  if (out_name && n_core == 1) {
     FILE *f = std::fopen(out_name, "wb");
     std::fwrite(column.data(), sizeof(double), column.size(), f);
     std::fclose(f);
+  } else if (out_name) {   // <out>.<rank>: the local cells' ids before partitioning, then their coefficients
+    part.GatherSolutions();
+    FILE *f = std::fopen((std::string(out_name) + "." + std::to_string(i_core)).c_str(), "wb");
+    int64_t n = part.CountLocalCells();
+    std::fwrite(&n, sizeof(n), 1, f);
+    for (auto const &cell : part.GetLocalCells()) { int64_t g = cell.metis_id; std::fwrite(&g, sizeof(g), 1, f); }
+    std::fwrite(part.cell_data().data(), sizeof(double), part.cell_data().size(), f);
+    std::fclose(f);
   }
+  MPI_Finalize();                             // sourceless.cpp:227
   return 0;
 }

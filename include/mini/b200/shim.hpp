@@ -32,6 +32,7 @@
 #include <vector>
 
 #include "minicfd_b200.h"
+#include "mini/b200/comm.hpp"
 
 namespace mini {
 
@@ -254,6 +255,55 @@ inline void Check(int status, mcfd_ctx *ctx, const char *what) {
     throw std::runtime_error(std::string(what) + ": " + mcfd_last_error(ctx));
   }
 }
+
+// Wire the context of this rank's part to the contexts of the neighbouring parts, one process per part
+// (minicfd_b200.h, "peer" section; the same hand-shake as minicfd_b200/peer.py): every rank publishes the CUDA IPC
+// handles of its epoch words, time-step slots and receive stage together with its neighbour list, opens what its
+// neighbours published, and connects.  Collective.  Halo: parts / send_counts / recv_counts as given to SetMesh.
+template <class Halo>
+void PeerConnect(mcfd_ctx *ctx, Halo const &halo, Comm &comm) {
+  constexpr int kMaxNeighbours = 32;
+  struct Card {
+    mcfd_ipc_handle handles[3];
+    int32_t n_neighbours;
+    int32_t neighbours[kMaxNeighbours];
+    int64_t recv_counts[kMaxNeighbours];
+  };
+  static_assert(sizeof(Card) <= Comm::kBlockBytes);
+  const int world = comm.size(), rank = comm.rank(), n = (int)halo.parts.size();
+  if (n > kMaxNeighbours) throw std::runtime_error("PeerConnect: more than 32 neighbouring parts");
+  Card mine{};
+  void *own[3];
+  Check(mcfd_peer_export(ctx, world, mine.handles, own), ctx, "mcfd_peer_export");
+  mine.n_neighbours = n;
+  for (int i = 0; i < n; ++i) { mine.neighbours[i] = (int32_t)halo.parts[i]; mine.recv_counts[i] = halo.recv_counts[i]; }
+  std::vector<Card> all(world);
+  comm.Allgather(&mine, sizeof(Card), all.data());
+  std::vector<std::array<void *, 3>> opened(world, {nullptr, nullptr, nullptr});
+  auto pointer = [&](int r, int which) {
+    if (r == rank) return own[which];
+    if (!opened[r][which]) Check(mcfd_peer_open(ctx, &all[r].handles[which], &opened[r][which]), ctx, "mcfd_peer_open");
+    return opened[r][which];
+  };
+  std::vector<void *> flags(n), recv(n), world_flags(world), world_slots(world);
+  std::vector<int32_t> slot(n);
+  std::vector<int64_t> items(n), offset(n);
+  for (int i = 0; i < n; ++i) {
+    const Card &q = all[halo.parts[i]];
+    int there = -1;
+    for (int j = 0; j < q.n_neighbours; ++j) if (q.neighbours[j] == rank) there = j;
+    if (there < 0 || q.recv_counts[there] != halo.send_counts[i]) throw std::runtime_error("PeerConnect: the send / recv lists of two parts disagree");
+    flags[i] = pointer((int)halo.parts[i], 0);
+    recv[i] = pointer((int)halo.parts[i], 2);
+    slot[i] = there;
+    items[i] = 0;
+    for (int j = 0; j < q.n_neighbours; ++j) { if (j == there) offset[i] = items[i]; items[i] += q.recv_counts[j]; }
+  }
+  for (int r = 0; r < world; ++r) { world_flags[r] = pointer(r, 0); world_slots[r] = pointer(r, 1); }
+  Check(mcfd_peer_connect(ctx, rank, world, n, flags.data(), slot.data(), recv.data(), items.data(), offset.data(),
+      world_flags.data(), world_slots.data()), ctx, "mcfd_peer_connect");
+  comm.Barrier();   // nobody delivers before everybody is connected
+}
 }  // namespace b200
 
 namespace mesh {
@@ -274,15 +324,44 @@ class Part {
   static constexpr int kDegrees = Poly::P;
   static constexpr int kComponents = Poly::K;
   static constexpr int kFields = Poly::kFields;
-  struct Cell {   // only what drivers name: `mini::limiter::weno::Lazy<Cell>` (demo/euler/sourceless.hpp:78) and the
-    using Polynomial = Poly;   // id a cell-data callback of the VTK writer asks for (sourceless.cpp:122-126)
+  // Host-side views of the part's cells and boundary faces (part.hpp:186-291, 97-184): the geometry a driver or a
+  // callback asks for.  The polynomial coefficients live on the device; GatherSolutions() brings them to the host
+  // array that WriteSolutions / the cell views read (part.hpp:380-387, 1052-1069).
+  class Cell {
+   public:
+    using Polynomial = Poly;
     using Scalar = typename Poly::Scalar;
     using Global = typename Poly::Global;
     using Value = typename Poly::Value;
-    Int id() const { return id_; }
+    Int metis_id = -1;                                      // part.hpp:190: the cell's id before partitioning
+    Int id() const { return id_; }                          // part.hpp:245
+    bool inner() const { return inner_; }                   // part.hpp:248
+    bool inter() const { return !inner_; }                  // part.hpp:251
+    Global const &center() const { return center_; }        // part.hpp:254, coordinate/hexahedron.hpp center()
+    Scalar volume() const { return volume_; }               // part.hpp:242
+    Scalar length() const { return length_; }               // part.hpp:239: cbrt(volume) / 2
+    int CountCorners() const { return 8; }                  // part.hpp:277
+    int CountFields() const { return Poly::kFields; }       // part.hpp:280
+    // the gathered coefficients of this cell, [N][K] (nodal schemes) or [K][M] (modal), after Part::GatherSolutions()
+    Scalar const *coeff() const { return coeff_; }
     Int id_ = -1;
+    bool inner_ = true;
+    Global center_{};
+    Scalar volume_ = 0, length_ = 0;
+    Scalar const *coeff_ = nullptr;
   };
-  struct Face {};  // named by the lambda handed to weno::Eigen::InstallRiemannSolvers (demo/euler/rotorcraft.cpp:93-96)
+  class Face {   // boundary faces: holder only (part.hpp:97-184)
+   public:
+    Int id() const { return id_; }                          // part.hpp:162
+    Global const &center() const { return center_; }        // part.hpp:148
+    Scalar area() const { return area_; }                   // part.hpp:151
+    Cell const &holder() const { return *holder_; }         // part.hpp:165
+    Cell const *other(Cell const *cell) const { return cell == holder_ ? nullptr : holder_; }
+    Int id_ = -1;
+    Global center_{};
+    Scalar area_ = 0;
+    Cell const *holder_ = nullptr;
+  };
 
   struct Halo {
     std::vector<int64_t> parts, send_counts, send_cells, recv_counts, recv_cells;
@@ -296,12 +375,18 @@ class Part {
       std::vector<int64_t> bface_nodes, std::vector<std::string> const &bface_names, Halo halo = Halo()) {
     nodes_ = std::move(nodes); cell_nodes_ = std::move(cell_nodes);
     n_local_ = n_local; n_ghost_ = n_ghost; bface_nodes_ = std::move(bface_nodes); halo_ = std::move(halo);
+    cells_built_ = false;
     bface_tags_.clear();
     for (auto const &name : bface_names) {
       auto it = name_to_tag_.find(name);
       if (it == name_to_tag_.end()) it = name_to_tag_.emplace(name, (int32_t)name_to_tag_.size()).first;
       bface_tags_.push_back(it->second);
     }
+  }
+  // The boundary sections of the whole mesh: a part knows every section of its zone, also those it has no face of
+  // (part.hpp:1456-1549 reads all of them from the file).  Call before SetMesh.
+  void DeclareSections(std::vector<std::string> const &names) {
+    for (auto const &name : names) if (!name_to_tag_.count(name)) name_to_tag_.emplace(name, (int32_t)name_to_tag_.size());
   }
   int mpi_rank() const { return rank_; }
   int mpi_size() const { return size_; }
@@ -322,6 +407,52 @@ class Part {
   Int GetCellDataOffset(Int i_cell) const { return i_cell * kFields; }  // part.hpp:784-787
   Int GetCellDataSize() const { return n_local_ * kFields; }            // part.hpp:793-797
   bool IsLocal(Int i_cell) const { return 0 <= i_cell && i_cell < n_local_; }
+  bool IsGhost(Int i_cell) const { return n_local_ <= i_cell && i_cell < n_local_ + n_ghost_; }   // part.hpp:1048
+  // the cells' ids before partitioning (Cell::metis_id, part.hpp:190), local then ghost; optional
+  void SetCellGlobalIds(std::vector<int64_t> ids) { global_ids_ = std::move(ids); cells_built_ = false; }
+
+  // part.hpp:1330-1365.  Local cells in id order: inner cells (no ghost neighbour) first, then inter cells.
+  std::vector<Cell> const &GetLocalCells() const { BuildCells(); return cells_; }
+  std::vector<Cell *> const &GetInnerCellPointers() { BuildCells(); return inner_ptrs_; }
+  std::vector<Cell *> const &GetInterCellPointers() { BuildCells(); return inter_ptrs_; }
+  Cell const &GetCell(Int i_cell) const { BuildCells(); return cells_.at(i_cell); }
+  // part.hpp:1399-1409: the faces of the boundary section `name`, in the order of the boundary face table
+  std::vector<Face> const &GetBoundaryFaces(std::string const &name) const {
+    BuildCells();
+    auto it = bfaces_by_name_.find(name);
+    if (it == bfaces_by_name_.end()) throw std::runtime_error("no boundary section named " + name);
+    return it->second;
+  }
+
+  // part.hpp:1273-1314.  The coefficients of the send cells travel to the neighbouring parts' ghost cells: here
+  // between the GPUs, enqueued on the context's stream (mcfd_peer_push / mcfd_peer_wait); every rank calls both.
+  void ShareGhostCellCoeffs() {
+    if (n_ghost_ == 0) return;
+    RequireContext("ShareGhostCellCoeffs");
+    b200::Check(mcfd_peer_push(context_), context_, "mcfd_peer_push");
+  }
+  void UpdateGhostCellCoeffs() {
+    if (n_ghost_ == 0) return;
+    RequireContext("UpdateGhostCellCoeffs");
+    b200::Check(mcfd_peer_wait(context_), context_, "mcfd_peer_wait");
+  }
+  // part.hpp:1052-1069: polynomial coefficients -> the per-cell data array a frame is written from, and back
+  void GatherSolutions() {
+    RequireContext("GatherSolutions");
+    cell_data_.resize((size_t)GetCellDataSize());
+    b200::Check(mcfd_get_solution(context_, cell_data_.data()), context_, "mcfd_get_solution");
+    BuildCells();
+    for (Int c = 0; c < n_local_; ++c) cells_[c].coeff_ = cell_data_.data() + GetCellDataOffset(c);
+  }
+  void ScatterSolutions() {
+    RequireContext("ScatterSolutions");
+    if ((Int)cell_data_.size() != GetCellDataSize()) throw std::runtime_error("ScatterSolutions: nothing gathered or read");
+    b200::Check(mcfd_set_solution(context_, cell_data_.data()), context_, "mcfd_set_solution");
+    ShareGhostCellCoeffs();
+    UpdateGhostCellCoeffs();
+  }
+  std::vector<Scalar> &cell_data() { return cell_data_; }
+  std::vector<Scalar> const &cell_data() const { return cell_data_; }
   int32_t TagOf(std::string const &name) const {
     auto it = name_to_tag_.find(name);
     if (it == name_to_tag_.end()) throw std::runtime_error("no boundary section named " + name);
@@ -342,8 +473,71 @@ class Part {
     return g;
   }
 
+  void RequireContext(const char *what) const {
+    if (!context_) throw std::runtime_error(std::string(what) + ": no spatial object has been built on this part yet");
+  }
+  // the host views: centres from the vertices, volume and length from the library (the reference's own quadrature,
+  // part.hpp:230-232), inner / inter from the send lists (part.hpp:746-767)
+  void BuildCells() const {
+    if (cells_built_ && cells_context_ == context_) return;
+    cells_.assign((size_t)n_local_, Cell());
+    std::vector<double> length, volume;
+    if (context_) {
+      length.resize((size_t)n_local_); volume.resize((size_t)n_local_);
+      b200::Check(mcfd_get_cell_geometry(context_, length.data(), volume.data()), context_, "mcfd_get_cell_geometry");
+    }
+    for (Int c = 0; c < n_local_; ++c) {
+      Cell &cell = cells_[c];
+      cell.id_ = c;
+      cell.metis_id = global_ids_.empty() ? c : (Int)global_ids_[c];
+      for (int v = 0; v < 8; ++v) for (int d = 0; d < 3; ++d) cell.center_[d] += nodes_[cell_nodes_[c * 8 + v] * 3 + d] / 8;
+      if (context_) { cell.volume_ = volume[c]; cell.length_ = length[c]; }
+    }
+    for (int64_t s : halo_.send_cells) cells_[s].inner_ = false;
+    inner_ptrs_.clear(); inter_ptrs_.clear();
+    for (auto &cell : cells_) (cell.inner_ ? inner_ptrs_ : inter_ptrs_).push_back(&cell);
+    bfaces_by_name_.clear();
+    for (auto const &kv : name_to_tag_) bfaces_by_name_[kv.first];
+    std::unordered_map<int32_t, std::string> name_of;
+    for (auto const &kv : name_to_tag_) name_of[kv.second] = kv.first;
+    // the holder of a boundary quad: the local cell that has its four nodes
+    std::unordered_map<int64_t, std::vector<Int>> cells_of_node;
+    for (Int c = 0; c < n_local_; ++c) for (int v = 0; v < 8; ++v) cells_of_node[cell_nodes_[c * 8 + v]].push_back(c);
+    static const double gx[3] = {-0.7745966692414834, 0.0, 0.7745966692414834}, gw[3] = {5.0 / 9, 8.0 / 9, 5.0 / 9};
+    for (size_t f = 0; f < bface_tags_.size(); ++f) {
+      Face face;
+      face.id_ = (Int)f;
+      const int64_t *q = &bface_nodes_[f * 4];
+      double x[4][3];
+      for (int v = 0; v < 4; ++v) for (int d = 0; d < 3; ++d) { x[v][d] = nodes_[q[v] * 3 + d]; face.center_[d] += x[v][d] / 4; }
+      for (int a = 0; a < 3; ++a) for (int b = 0; b < 3; ++b) {   // |dx/da x dx/db| of the bilinear quad, 3 x 3 Gauss points
+        double da[3], db[3];
+        for (int d = 0; d < 3; ++d) {
+          da[d] = ((1 - gx[b]) * (x[1][d] - x[0][d]) + (1 + gx[b]) * (x[2][d] - x[3][d])) / 4;
+          db[d] = ((1 - gx[a]) * (x[3][d] - x[0][d]) + (1 + gx[a]) * (x[2][d] - x[1][d])) / 4;
+        }
+        const double n[3] = {da[1] * db[2] - da[2] * db[1], da[2] * db[0] - da[0] * db[2], da[0] * db[1] - da[1] * db[0]};
+        face.area_ += gw[a] * gw[b] * std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+      }
+      for (Int c : cells_of_node[q[0]]) {
+        int hit = 0;
+        for (int v = 0; v < 8; ++v) for (int m = 0; m < 4; ++m) hit += cell_nodes_[c * 8 + v] == q[m];
+        if (hit == 4) { face.holder_ = &cells_[c]; break; }
+      }
+      bfaces_by_name_[name_of[bface_tags_[f]]].push_back(face);
+    }
+    cells_built_ = true;
+    cells_context_ = context_;
+  }
+
   std::vector<Scalar> nodes_;
-  std::vector<int64_t> cell_nodes_, bface_nodes_;
+  std::vector<int64_t> cell_nodes_, bface_nodes_, global_ids_;
+  std::vector<Scalar> cell_data_;
+  mutable std::vector<Cell> cells_;
+  mutable std::vector<Cell *> inner_ptrs_, inter_ptrs_;
+  mutable std::map<std::string, std::vector<Face>> bfaces_by_name_;
+  mutable bool cells_built_ = false;
+  mutable mcfd_ctx *cells_context_ = nullptr;
   std::vector<int32_t> bface_tags_;
   std::unordered_map<std::string, int32_t> name_to_tag_;
   Halo halo_;
@@ -467,6 +661,10 @@ class FiniteElementB200 : public temporal::System<typename P::Scalar> {
       auto &h = p.halo_;
       b200::Check(mcfd_set_halo(ctx_, (int32_t)h.send_counts.size(), h.send_counts.data(), h.send_cells.data(),
           (int32_t)h.recv_counts.size(), h.recv_counts.data(), h.recv_cells.data()), ctx_, "mcfd_set_halo");
+      if (p.mpi_size() > 1) {   // one process per part: the ghost exchange runs between the GPUs
+        b200::PeerConnect(ctx_, h, b200::Comm::World());
+        peer_connected_ = true;
+      }
     }
     b200::Check(mcfd_set_time_callback(ctx_, &FiniteElementB200::OnTime, this), ctx_, "mcfd_set_time_callback");
     p.context_ = ctx_;
@@ -540,16 +738,32 @@ class FiniteElementB200 : public temporal::System<typename P::Scalar> {
     b200::Check(mcfd_get_solution(ctx_, column.data()), ctx_, "mcfd_get_solution");
     return column;
   }
-  Column GetResidualColumn() const override {
+  Column GetResidualColumn() const override {   // fem.hpp:248-258
     Column column(part().GetCellDataSize());
     PushDiffusion();
+    if (peer_connected_) {
+      part_ptr_->ShareGhostCellCoeffs();
+      part_ptr_->UpdateGhostCellCoeffs();
+    }
     b200::Check(mcfd_residual(ctx_, t_curr_, column.data(), nullptr), ctx_, "mcfd_residual");
     return column;
   }
   bool FusedUpdate(int order, double t_curr, double dt) override {
-    if (part().CountGhostCells() > 0) return false;   // parts with ghosts are driven stage by stage
     PushDiffusion();
-    b200::Check(mcfd_rk_step(ctx_, order, t_curr, dt), ctx_, "mcfd_rk_step");
+    if (part().CountGhostCells() == 0) {
+      b200::Check(mcfd_rk_step(ctx_, order, t_curr, dt), ctx_, "mcfd_rk_step");
+      return true;
+    }
+    if (!peer_connected_) return false;   // ghosts filled by the host: driven residual by residual
+    // every stage: deliver the stage input's send cells, advance the inner cells meanwhile, then the inter cells
+    // (fem.hpp:249-256 with the exchange of part.hpp:1273-1314 between the GPUs)
+    b200::Check(mcfd_rk_begin(ctx_, order, t_curr, dt), ctx_, "mcfd_rk_begin");
+    for (int stage = 0; stage < order; ++stage) {
+      part_ptr_->ShareGhostCellCoeffs();
+      b200::Check(mcfd_rk_stage_inner(ctx_, stage), ctx_, "mcfd_rk_stage_inner");
+      part_ptr_->UpdateGhostCellCoeffs();
+      b200::Check(mcfd_rk_stage_inter(ctx_, stage), ctx_, "mcfd_rk_stage_inter");
+    }
     return true;
   }
   Scalar GetTimeStep(Scalar dt_guess, int rk_order) const {  // fem.hpp:417-435, fr/lobatto.hpp:220-222
@@ -603,6 +817,7 @@ class FiniteElementB200 : public temporal::System<typename P::Scalar> {
 
   Part *part_ptr_;
   mcfd_ctx *ctx_ = nullptr;
+  bool peer_connected_ = false;
   double t_curr_ = 0;
   std::map<int32_t, Bc> bcs_;
 };

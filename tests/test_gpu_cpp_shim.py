@@ -15,6 +15,7 @@ from minicfd_b200 import mesh as meshmod
 
 pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+NOMPI = os.path.join(ROOT, "include", "mini", "b200", "nompi")   # the drivers' MPI calls without an MPI library
 
 
 def _sod_reference(riemann, n_steps, limiter=False, eigen=False, degree=2, perturb=None):
@@ -64,7 +65,7 @@ def _sod_reference(riemann, n_steps, limiter=False, eigen=False, degree=2, pertu
 @pytest.mark.parametrize("flag,riemann,tol", [("-DUSE_HLLC", 1, 1e-12), ("", 0, 1e-9)])
 def test_sod_driver_through_cpp_template_api(tmp_path, flag, riemann, tol):
     exe = tmp_path / "shock_tube"
-    cmd = ["g++", "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"),
+    cmd = ["g++", "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"), "-I", NOMPI,
            os.path.join(ROOT, "demo", "euler", "shock_tube.cpp"), "-o", str(exe),
            "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200",
            "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")]
@@ -89,7 +90,7 @@ def test_sod_driver_with_weno_limiter_through_cpp_template_api(tmp_path, eigen):
     demo/euler/sourceless.hpp:41-80 and sourceless.cpp:114-120 spell them; the limiter runs after Approximate and
     after every Runge-Kutta stage."""
     exe = tmp_path / "shock_tube_weno"
-    subprocess.check_call(["g++", "-DUSE_HLLC", "-DLIMITER", *(["-DEIGEN_LIMITER"] if eigen else []), "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"),
+    subprocess.check_call(["g++", "-DUSE_HLLC", "-DLIMITER", *(["-DEIGEN_LIMITER"] if eigen else []), "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"), "-I", NOMPI,
                            os.path.join(ROOT, "demo", "euler", "shock_tube.cpp"), "-o", str(exe),
                            "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200",
                            "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")])
@@ -147,7 +148,7 @@ def test_sod_driver_at_degree_three(tmp_path, limiter):
     compare with (this library returns NaN there)."""
     exe = tmp_path / "shock_tube_p3"
     subprocess.check_call(["g++", "-DUSE_HLLC", "-DDEGREE=3", *(["-DLIMITER"] if limiter else []), "-std=c++20", "-O2",
-                           "-I", os.path.join(ROOT, "include"), os.path.join(ROOT, "demo", "euler", "shock_tube.cpp"),
+                           "-I", os.path.join(ROOT, "include"), "-I", NOMPI, os.path.join(ROOT, "demo", "euler", "shock_tube.cpp"),
                            "-o", str(exe), "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200",
                            "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")])
     out = tmp_path / "column.bin"
@@ -172,7 +173,7 @@ def test_sod_driver_with_energy_based_viscosity_through_cpp_template_api(tmp_pat
     if ref is None:
         pytest.skip("oracle/_ref not shipped")
     exe = tmp_path / "shock_tube_viscosity"
-    subprocess.check_call(["g++", "-DUSE_HLLC", "-DVISCOSITY", *(["-DAS_SHIPPED"] if as_shipped else []), "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"),
+    subprocess.check_call(["g++", "-DUSE_HLLC", "-DVISCOSITY", *(["-DAS_SHIPPED"] if as_shipped else []), "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"), "-I", NOMPI,
                            os.path.join(ROOT, "demo", "euler", "shock_tube.cpp"), "-o", str(exe),
                            "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200",
                            "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")])
@@ -221,7 +222,7 @@ def test_sod_driver_dgfem_through_cpp_template_api(tmp_path, limiter):
     if ref is None:
         pytest.skip("oracle/_ref not shipped")
     exe = tmp_path / "shock_tube_dgfem"
-    subprocess.check_call(["g++", "-DUSE_HLLC", "-DDGFEM", *(["-DLIMITER"] if limiter else []), "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"),
+    subprocess.check_call(["g++", "-DUSE_HLLC", "-DDGFEM", *(["-DLIMITER"] if limiter else []), "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"), "-I", NOMPI,
                            os.path.join(ROOT, "demo", "euler", "shock_tube.cpp"), "-o", str(exe),
                            "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200",
                            "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")])
@@ -357,7 +358,7 @@ def test_double_mach_driver_through_cpp_template_api(tmp_path):
     if not refapi.available(2):
         pytest.skip("oracle/_ref not shipped")
     exe = tmp_path / "double_mach"
-    subprocess.check_call(["g++", "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"),
+    subprocess.check_call(["g++", "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"), "-I", NOMPI,
                            os.path.join(ROOT, "demo", "euler", "double_mach.cpp"), "-o", str(exe),
                            "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200",
                            "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")])
@@ -437,7 +438,7 @@ def test_blasius_driver_through_cpp_template_api(tmp_path):
     if not refapi.available(2):
         pytest.skip("oracle/_ref not shipped")
     exe = tmp_path / "blasius"
-    subprocess.check_call(["g++", "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"),
+    subprocess.check_call(["g++", "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"), "-I", NOMPI,
                            os.path.join(ROOT, "demo", "laminar", "blasius.cpp"), "-o", str(exe),
                            "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200",
                            "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")])
@@ -449,3 +450,86 @@ def test_blasius_driver_through_cpp_template_api(tmp_path):
     assert got.shape == ref.shape == (8 * 8 * 3 * 135,)
     assert np.isfinite(ref).all()
     assert np.abs(got - ref).max() / np.abs(ref).max() < 1e-12
+
+
+def _run_ranks(exe, args, world, tmp_path, timeout=600):
+    """One process per part, like `mpirun -n <world>`: rank and size through the environment (mini/b200/comm.hpp)."""
+    import torch
+    n_dev = torch.cuda.device_count()
+    procs = []
+    for r in range(world):
+        env = dict(os.environ, MCFD_SESSION=f"t{os.getpid()}_{tmp_path.name}"[:60], MCFD_WORLD_SIZE=str(world), MCFD_RANK=str(r))
+        if n_dev >= world:                      # one GPU per rank where the box has them; else the ranks share GPU 0
+            env["CUDA_VISIBLE_DEVICES"] = str(r)
+        procs.append(subprocess.Popen([str(exe), *args], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+    outs = []
+    for p in procs:
+        try:
+            outs.append(p.communicate(timeout=timeout)[0])
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise
+    for r, p in enumerate(procs):
+        assert p.returncode == 0, f"rank {r}: {outs[r]}"
+    return outs
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_sod_driver_one_process_per_part(tmp_path, world):
+    """The driver's loop of demo/euler/sourceless.cpp:187-215 with one process per part: GetTimeStep,
+    MPI_Allreduce(MIN) (nompi/mpi.h), RungeKutta::Update whose residuals see the neighbouring part through
+    Part::ShareGhostCellCoeffs / UpdateGhostCellCoeffs (part.hpp:1273-1314) — here device-to-device copies set up by
+    b200::PeerConnect over CUDA IPC.  The gathered parts (Part::GatherSolutions, Cell::metis_id) against the
+    reference's own code on the whole mesh."""
+    exe = tmp_path / "shock_tube"
+    subprocess.check_call(["g++", "-DUSE_HLLC", "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"), "-I", NOMPI,
+                           os.path.join(ROOT, "demo", "euler", "shock_tube.cpp"), "-o", str(exe),
+                           "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200", "-lrt",
+                           "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")])
+    out = tmp_path / "column.bin"
+    n_steps = 10
+    _run_ranks(exe, [str(n_steps), str(out)], world, tmp_path)
+    got = np.full((300, 135), np.nan)
+    for r in range(world):
+        raw = np.fromfile(f"{out}.{r}", dtype=np.uint8)
+        n = int(raw[:8].view(np.int64)[0])
+        ids = raw[8:8 + 8 * n].view(np.int64)
+        got[ids] = raw[8 + 8 * n:].view(np.float64).reshape(n, 135)
+    assert np.isfinite(got).all()              # every cell owned by exactly one part
+    ref = _sod_reference(1, n_steps)
+    assert np.abs(got.reshape(-1) - ref).max() / np.abs(ref).max() < 1e-12
+
+
+def test_part_surface(tmp_path):
+    """Part::GetLocalCells / GetInner|InterCellPointers / GetBoundaryFaces(name), Cell::{id, metis_id, center, volume,
+    length, inner}, Face::{center, area, holder}, GatherSolutions / ScatterSolutions (part.hpp:186-291, 1052-1069,
+    1330-1409) on a stretched box, against plain arithmetic."""
+    exe = tmp_path / "part_surface"
+    subprocess.check_call(["g++", "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"), "-I", NOMPI,
+                           os.path.join(ROOT, "tests", "drivers", "part_surface.cpp"), "-o", str(exe),
+                           "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200",
+                           "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")])
+    res = subprocess.run([str(exe)], capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout + res.stderr
+    lines = res.stdout.splitlines()
+    xs, ys, zs = np.array([0, 0.5, 1.5, 3.0, 3.5]), np.array([0, 1.0, 3]), np.array([0, 0.25, 0.5, 1.5])
+    assert lines[0] == "local 24 ghost 0 inner 24 inter 0"
+    cells = [l.split() for l in lines if l.startswith("cell ")]
+    assert len(cells) == 24
+    for c in cells:
+        g = int(c[1]); i, j, k = g % 4, (g // 4) % 2, g // 8
+        assert int(c[2]) == g and int(c[8]) == 1 and int(c[9]) == 135
+        centre = [(xs[i] + xs[i + 1]) / 2, (ys[j] + ys[j + 1]) / 2, (zs[k] + zs[k + 1]) / 2]
+        vol = (xs[i + 1] - xs[i]) * (ys[j + 1] - ys[j]) * (zs[k + 1] - zs[k])
+        np.testing.assert_allclose([float(v) for v in c[3:6]], centre, rtol=1e-15, atol=1e-15)
+        assert abs(float(c[6]) - vol) < 1e-14 * vol and abs(float(c[7]) - 0.5 * vol ** (1 / 3)) < 1e-14   # part.hpp:230-232
+    sections = {l.split()[1]: l.split()[2:] for l in lines if l.startswith("section ")}
+    assert int(sections["Left"][0]) == 6 and abs(float(sections["Left"][1]) - 3 * 1.5) < 1e-13 and abs(float(sections["Left"][2])) < 1e-14
+    assert int(sections["Right"][0]) == 6 and abs(float(sections["Right"][2]) - 3.5) < 1e-13
+    assert int(sections["Top"][0]) == 8 and abs(float(sections["Top"][1]) - 3.5 * 3) < 1e-13
+    assert int(sections["Front"][0]) == 12 and abs(float(sections["Front"][1]) - 3.5 * 1.5) < 1e-13
+    a, b = [float(v) for v in [l for l in lines if l.startswith("coeff ")][0].split()[1:]]
+    assert a == b
+    s = [float(v) for v in [l for l in lines if l.startswith("scattered ")][0].split()[1:]]
+    assert s[0] == 2 * a

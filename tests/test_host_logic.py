@@ -343,3 +343,20 @@ def test_kernel_source_fr_general(degree, c_next):
         bvals[tags == tag] = cases.bc_function(kind)(pts[tags == tag], 0.2)
     got = emuapi.stage(m, degree, 2, 1, u, tag_kinds=cases.MIXED_BCS, bvals=bvals, c_next=c_next)
     assert relerr(got, o.residual(u, 0.2)) < 1e-12
+
+
+@pytest.mark.parametrize("world", [1, 4])
+def test_nompi_allreduce_between_processes(tmp_path, world):
+    """include/mini/b200/nompi/mpi.h + comm.hpp: MPI_Allreduce(MIN | MAX | SUM), MPI_Barrier, rank and size between
+    real processes over POSIX shared memory — what the C++ drivers use where the reference calls MPI
+    (demo/euler/sourceless.cpp:60-66, 194)."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = tmp_path / "comm_check"
+    subprocess.check_call(["g++", "-std=c++20", "-O1", "-I", os.path.join(root, "include"),
+                           "-I", os.path.join(root, "include", "mini", "b200", "nompi"),
+                           os.path.join(root, "tests", "host_emulation", "comm_check.cpp"), "-o", str(exe), "-lrt"])
+    procs = [subprocess.Popen([str(exe)], env=dict(os.environ, MCFD_SESSION=f"c{os.getpid()}_{world}", MCFD_WORLD_SIZE=str(world),
+                                                   MCFD_RANK=str(r)), stdout=subprocess.PIPE, text=True) for r in range(world)]
+    for r, p in enumerate(procs):
+        out = p.communicate(timeout=120)[0]
+        assert p.returncode == 0 and f"rank {r} of {world} ok" in out, out
