@@ -451,6 +451,30 @@ class Part {
     ShareGhostCellCoeffs();
     UpdateGhostCellCoeffs();
   }
+  // part.hpp:1023-1037: sum over the local cells of the quadrature of |u - exact(x, t)|, per component (nodal schemes:
+  // the cell's own Lobatto rule, whose points are the nodes).  Gathers the solution first.
+  template <class Callable>
+  Value MeasureL1Error(Callable &&exact_solution, Scalar t_curr) {
+    static_assert(!requires { Poly::kModalOnly; }, "MeasureL1Error: nodal polynomials only");
+    GatherSolutions();
+    constexpr int Q = Poly::IntegratorX::Q, N = Poly::N, K = Poly::K;
+    const std::array<Scalar, 4> w = Q == 3 ? std::array<Scalar, 4>{1.0 / 3, 4.0 / 3, 1.0 / 3, 0} : std::array<Scalar, 4>{1.0 / 6, 5.0 / 6, 5.0 / 6, 1.0 / 6};
+    std::vector<double> det((size_t)n_local_ * N);
+    b200::Check(mcfd_get_jacobian_determinants(context_, det.data()), context_, "mcfd_get_jacobian_determinants");
+    Value l1_error{};
+    for (Int c = 0; c < n_local_; ++c) {
+      for (int q = 0; q < N; ++q) {
+        const Scalar d = det[(size_t)c * N + q], weight = w[q / (Q * Q)] * w[(q / Q) % Q] * w[q % Q] * d;
+        Value exact = exact_solution(NodeCoordinate(c, q), t_curr);
+        for (int k = 0; k < K; ++k) {
+          Scalar u = cell_data_[GetCellDataOffset(c) + q * K + k];
+          if constexpr (Poly::kLocal) u /= d;   // the coefficient is det(J) u (hexahedron.hpp:344-349)
+          l1_error[k] += std::abs(u - exact[k]) * weight;
+        }
+      }
+    }
+    return l1_error;
+  }
   std::vector<Scalar> &cell_data() { return cell_data_; }
   std::vector<Scalar> const &cell_data() const { return cell_data_; }
   int32_t TagOf(std::string const &name) const {
@@ -684,6 +708,7 @@ class FiniteElementB200 : public temporal::System<typename P::Scalar> {
     return none;
   }
   mcfd_ctx *context() const { return ctx_; }
+  bool peer_connected() const { return peer_connected_; }   // the ghost exchange runs between the GPUs (b200::PeerConnect)
 
   template <class Callable>
   void Approximate(Callable &&func) {  // fem.hpp:147-154
@@ -905,24 +930,41 @@ class WithLimiter : public ConcreteFiniteElement {
     Base::Approximate(std::forward<Callable>(func));
   }
   bool FusedUpdate(int order, double t_curr, double dt) override {
-    if (this->part().CountGhostCells() > 0) return false;
+    const bool ghosts = this->part().CountGhostCells() > 0;
+    if (ghosts && !this->peer_connected()) return false;
     mcfd_ctx *ctx = this->context();
     b200::Check(mcfd_rk_begin(ctx, order, t_curr, dt), ctx, "mcfd_rk_begin");
     for (int stage = 0; stage < order; ++stage) {
+      // the residual sees the neighbours' LIMITED coefficients (fem.hpp:249-256 after with_limiter.hpp:57-61)
+      if (ghosts) this->part_ptr()->ShareGhostCellCoeffs();
       b200::Check(mcfd_rk_stage_inner(ctx, stage), ctx, "mcfd_rk_stage_inner");
+      if (ghosts) this->part_ptr()->UpdateGhostCellCoeffs();
       b200::Check(mcfd_rk_stage_inter(ctx, stage), ctx, "mcfd_rk_stage_inter");
       Reconstruct();
     }
     return true;
   }
  private:
-  void Reconstruct() {   // mini::limiter::Reconstruct(part_ptr, limiter_ptr), limiter/reconstruct.hpp:21-54
-    if (!limiter_ptr_) return;
+  void Limit(int phase) {
     mcfd_ctx *ctx = this->context();
     if constexpr (Limiter::kEigen) {
-      b200::Check(mcfd_limiter_weno_eigen(ctx, limiter_ptr_->w0(), limiter_ptr_->eps(), -1), ctx, "mcfd_limiter_weno_eigen");
+      b200::Check(mcfd_limiter_weno_eigen(ctx, limiter_ptr_->w0(), limiter_ptr_->eps(), phase), ctx, "mcfd_limiter_weno_eigen");
     } else {
-      b200::Check(mcfd_limiter_weno_lazy(ctx, limiter_ptr_->w0(), limiter_ptr_->eps(), -1), ctx, "mcfd_limiter_weno_lazy");
+      b200::Check(mcfd_limiter_weno_lazy(ctx, limiter_ptr_->w0(), limiter_ptr_->eps(), phase), ctx, "mcfd_limiter_weno_lazy");
+    }
+  }
+  // mini::limiter::Reconstruct(part_ptr, limiter_ptr), limiter/reconstruct.hpp:21-54: the unlimited coefficients
+  // travel while the inner cells are limited; the inter cells then borrow the limited inner cells and the
+  // unlimited ghost cells
+  void Reconstruct() {
+    if (!limiter_ptr_) return;
+    if (this->part().CountGhostCells() > 0 && this->peer_connected()) {
+      this->part_ptr()->ShareGhostCellCoeffs();
+      Limit(0);
+      this->part_ptr()->UpdateGhostCellCoeffs();
+      Limit(1);
+    } else {
+      Limit(-1);
     }
   }
   Limiter *limiter_ptr_;
@@ -957,6 +999,10 @@ class EnergyBasedViscosity : public R {
     cache_valid_ = false;
   }
   // the ghost cells' values travel with mcfd_viscosity_halo_* where a host moves bytes between parts
+  // viscosity.hpp:163-189.  With one part there is nothing to exchange.  With several parts driven from C++ the cell
+  // viscosities would have to travel like the coefficients; that path exists on the Python host only
+  // (mcfd_viscosity_halo_*, minicfd_b200/spatial.py), so a multi-part C++ run is refused when it is built
+  // (WithViscosity's constructor) instead of running with stale ghost viscosities.
   static void ShareGhostCellProperties() {}
   static void UpdateGhostCellProperties() {}
   template <typename Int>
@@ -992,7 +1038,13 @@ class WithViscosity : public ConcreteFiniteElement {
   using Scalar = typename Base::Scalar;
   using Column = typename Base::Column;
   template <class... Args>
-  WithViscosity(Args &&...args) : Base(std::forward<Args>(args)...) { Riemann::Viscosity::Initialize(this); }
+  WithViscosity(Args &&...args) : Base(std::forward<Args>(args)...) {
+    if (this->part().CountGhostCells() > 0) {   // see EnergyBasedViscosity::ShareGhostCellProperties above
+      throw std::runtime_error("WithViscosity: parts with ghost cells are not served from C++ (the exchange of the "
+          "cell viscosities, with_viscosity.hpp:45-50, exists on the Python host only)");
+    }
+    Riemann::Viscosity::Initialize(this);
+  }
   void SetSolutionColumn(Column const &column) override {
     this->Base::SetSolutionColumn(column);
     Riemann::Viscosity::UpdateProperties();

@@ -166,7 +166,8 @@ int mcfd_halo_unpack(mcfd_ctx *ctx);
  * mcfd_peer_push delivers the send cells of the state the next residual reads (the current solution, or the stage input
  * inside an open RK step); mcfd_peer_wait holds the stream until every neighbour's delivery of the same count has
  * arrived and unpacks it into the ghost rows.  Every rank must push equally often, and again after every
- * mcfd_set_solution*.  mcfd_peer_min_time_step replaces the value in dt_dev (NULL: the context's own,
+ * mcfd_set_solution*; push and wait alternate (the same state may be pushed again after its wait — the limiter's
+ * unlimited, then limited coefficients: the receive stages keep a spare slot for that).  mcfd_peer_min_time_step replaces the value in dt_dev (NULL: the context's own,
  * mcfd_time_step_device) by the minimum over all ranks.  mcfd_peer_step is one whole GetTimeStep + MPI_Allreduce(MIN) +
  * RungeKutta<order>::Update (sourceless.cpp:191-196, rk.hpp:16-56) for the inviscid nodal schemes; the deliveries of
  * the stage results run on a stream of the context's own beside the next stage.  All counts live on the device, so

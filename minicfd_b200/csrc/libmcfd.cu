@@ -115,7 +115,9 @@ struct mcfd_ctx {
     DevBuf<unsigned long long> flags;            // [kPeerWords]: delivery counts per neighbour slot, then dt epochs per rank
     DevBuf<unsigned long long> counts;           // [kPeerCounts] peer.cuh: what the device keeps count of
     DevBuf<double> dt_slots;                     // [2][world]: every rank's time step, by step parity
-    DevBuf<double> send_stage, recv_stage;       // [3][fields][n_send | n_recv]: packed halo per state buffer
+    DevBuf<double> send_stage, recv_stage;       // [kPeerSlots][fields][n_send | n_recv]: packed halo per state buffer + a spare
+    int last_slot = -1;                          // where the latest delivery went (and the next reader looks)
+    bool last_plain = false;                     // ... and whether it was a mcfd_peer_push
     DevBuf<int> recv_index;                      // [n_ghost] ghost cell -> item of the receive stage
     DevBuf<int> tgt_offset, tgt_item;            // per local cell from first_inter on: its items of the send stage
     std::vector<double *> nbr_recv;              // [n_neighbours] the neighbour's receive stage, at this part's segment
@@ -1194,10 +1196,11 @@ int mcfd_peer_export(mcfd_ctx *ctx, int32_t world, mcfd_ipc_handle *handles, voi
   MCFD_CUDA(ctx, cudaMemset(pe.counts.p, 0, kPeerCounts * sizeof(unsigned long long)));
   MCFD_CUDA(ctx, pe.dt_slots.Alloc(2 * (size_t)world));
   MCFD_CUDA(ctx, cudaMemset(pe.dt_slots.p, 0, 2 * (size_t)world * sizeof(double)));
-  MCFD_CUDA(ctx, pe.recv_stage.Alloc(std::max<size_t>(1, 3 * n_recv * ctx->fields)));
-  MCFD_CUDA(ctx, pe.send_stage.Alloc(std::max<size_t>(1, 3 * n_send * ctx->fields)));
+  MCFD_CUDA(ctx, pe.recv_stage.Alloc(std::max<size_t>(1, kPeerSlots * n_recv * ctx->fields)));
+  MCFD_CUDA(ctx, pe.send_stage.Alloc(std::max<size_t>(1, kPeerSlots * n_send * ctx->fields)));
   MCFD_CUDA(ctx, cudaMemset(pe.recv_stage.p, 0, pe.recv_stage.n * sizeof(double)));
   pe.pushed_once = false;
+  pe.last_slot = -1; pe.last_plain = false;
   pe.connected = false;
   pe.deliveries_this_step = 0;
   void *ptrs[3] = {pe.flags.p, pe.dt_slots.p, pe.recv_stage.p};
@@ -1320,10 +1323,10 @@ static int RequirePeer(mcfd_ctx *ctx) {
   return MCFD_OK;
 }
 
-static double *PeerStage3(DevBuf<double> &b, int buf) { return b.p + (size_t)buf * (b.n / 3); }
+static double *PeerStage3(DevBuf<double> &b, int slot) { return b.p + (size_t)slot * (b.n / kPeerSlots); }
 
-// steps 2 and 3 of a delivery (peer.cuh): the copies of send stage `buf` into the neighbours' receive stages `buf`,
-// then the signal.  add: the host's part of the count; bump_plain: this is a delivery by mcfd_peer_push.
+// steps 2 and 3 of a delivery (peer.cuh): the copies of send stage `buf` (a slot) into the neighbours' receive stages
+// of the same slot, then the signal.  add: the host's part of the count; bump_plain: this is a delivery by mcfd_peer_push.
 static int PeerCopyAndSignal(mcfd_ctx *ctx, cudaStream_t stream, int buf, int bump_plain, int add) {
   auto &pe = ctx->peer;
   const size_t n_send = ctx->send_cells.n;
@@ -1338,27 +1341,29 @@ static int PeerCopyAndSignal(mcfd_ctx *ctx, cudaStream_t stream, int buf, int bu
   PeerSignalKernel<<<1, kPeerMaxNeighbours, 0, stream>>>(pe.flag_dev.p, pe.n_neighbours, pe.counts.p, bump_plain, add);
   MCFD_CUDA(ctx, cudaGetLastError());
   ctx->launches++;
+  pe.last_slot = buf;
+  pe.last_plain = bump_plain != 0;
   return MCFD_OK;
 }
 
-static int LaunchPeerPack(mcfd_ctx *ctx, cudaStream_t stream, int buf) {
+static int LaunchPeerPack(mcfd_ctx *ctx, cudaStream_t stream, int buf, int slot) {
   auto &pe = ctx->peer;
   const int n = (int)ctx->send_cells.n;
   if (!n) return MCFD_OK;
   const long long work = (long long)n * ctx->fields;
   PeerPackKernel<<<(int)std::min<long long>(1184, (work + 255) / 256), 256, 0, stream>>>(ctx->u[buf].p, ctx->fields,
-      ctx->send_cells.p, n, PeerStage3(pe.send_stage, buf));
+      ctx->send_cells.p, n, PeerStage3(pe.send_stage, slot));
   MCFD_CUDA(ctx, cudaGetLastError());
   ctx->launches++;
   return MCFD_OK;
 }
-static int LaunchPeerUnpack(mcfd_ctx *ctx, cudaStream_t stream, int buf) {
+static int LaunchPeerUnpack(mcfd_ctx *ctx, cudaStream_t stream, int buf, int slot) {
   auto &pe = ctx->peer;
   const int n = (int)ctx->recv_cells.n;
   if (!n) return MCFD_OK;
   const long long work = (long long)n * ctx->fields;
   PeerUnpackKernel<<<(int)std::min<long long>(1184, (work + 255) / 256), 256, 0, stream>>>(ctx->u[buf].p, ctx->fields,
-      ctx->recv_cells.p, n, PeerStage3(pe.recv_stage, buf));
+      ctx->recv_cells.p, n, PeerStage3(pe.recv_stage, slot));
   MCFD_CUDA(ctx, cudaGetLastError());
   ctx->launches++;
   return MCFD_OK;
@@ -1370,9 +1375,14 @@ int mcfd_peer_push(mcfd_ctx *ctx) {
   pe.pushed_once = true;
   if (pe.n_neighbours == 0) return MCFD_OK;
   const int buf = ctx->rk_order ? ctx->rk_in : ctx->cur;
-  if (int s = LaunchPeerPack(ctx, ctx->stream, buf)) return s;
+  // A second push of the same buffer in a row (the limited state after the unlimited one, a new solution written over
+  // the old one) must not land on the slot the neighbour may still be unpacking: it takes the spare slot.  The slot
+  // before that one is free again, because this rank's wait in between needed the neighbour's later push, which that
+  // neighbour enqueued behind its unpack.
+  const int slot = (pe.last_plain && pe.last_slot == buf) ? kPeerSpareSlot : buf;
+  if (int s = LaunchPeerPack(ctx, ctx->stream, buf, slot)) return s;
   // the count goes on from the stage deliveries of the last step, which the device adds up at the next step only
-  return PeerCopyAndSignal(ctx, ctx->stream, buf, 1, pe.deliveries_this_step);
+  return PeerCopyAndSignal(ctx, ctx->stream, slot, 1, pe.deliveries_this_step);
 }
 
 int mcfd_peer_wait(mcfd_ctx *ctx) {
@@ -1385,7 +1395,7 @@ int mcfd_peer_wait(mcfd_ctx *ctx) {
       pe.deliveries_this_step, pe.error.p);
   MCFD_CUDA(ctx, cudaGetLastError());
   ctx->launches++;
-  return LaunchPeerUnpack(ctx, ctx->stream, buf);
+  return LaunchPeerUnpack(ctx, ctx->stream, buf, pe.last_slot);
 }
 
 static int PeerDtPublish(mcfd_ctx *ctx, double *dt_dev) {
@@ -1426,7 +1436,7 @@ static int PeerStage(mcfd_ctx *ctx, int stage) {
   int status = mcfd_peer_wait(ctx);
   if (status == MCFD_OK) status = mcfd_rk_stage_inter(ctx, stage);
   const int buf = ctx->rk_order ? ctx->rk_in : ctx->cur;        // the stage's output
-  if (status == MCFD_OK) status = LaunchPeerPack(ctx, pe.side, buf);
+  if (status == MCFD_OK) status = LaunchPeerPack(ctx, pe.side, buf, buf);
   if (status == MCFD_OK) status = PeerCopyAndSignal(ctx, pe.side, buf, 0, ++pe.deliveries_this_step);
   ctx->stream = main;
   if (status != MCFD_OK) return status;
@@ -1453,7 +1463,7 @@ static int PeerFusedStage(mcfd_ctx *ctx, int stage) {
   f.wait_add = pe.deliveries_this_step;
   f.n_send = (int)ctx->send_cells.n; f.n_recv = (int)ctx->recv_cells.n;
   f.flags = pe.flags.p; f.counts = pe.counts.p;
-  f.recv = PeerStage3(pe.recv_stage, in); f.recv_index = pe.recv_index.p;
+  f.recv = PeerStage3(pe.recv_stage, pe.last_slot); f.recv_index = pe.recv_index.p;   // `in`, or the spare slot after a push
   f.send = PeerStage3(pe.send_stage, out); f.tgt_offset = pe.tgt_offset.p; f.tgt_item = pe.tgt_item.p;
   f.error = pe.error.p;
   cudaStream_t main = ctx->stream;

@@ -24,12 +24,17 @@
 // delivery follows a stage of the neighbour which itself had to wait for this part's delivery of the stage in
 // between — issued after this part finished reading X.  The send stage X is written by the stage with OUTPUT X and
 // read by the copies that follow it; the next writer is two stages later and waits for those copies (an event).
+// Outside a step (mcfd_peer_push / mcfd_peer_wait) the same buffer may be delivered twice in a row — the limiter's
+// unlimited then limited coefficients, a solution written over the previous one: the second delivery goes to a spare
+// fourth slot, so that two deliveries in a row never share a slot; the one before the previous is free by the
+// argument above (this rank's wait in between needed the neighbour's next push, enqueued behind its unpack).
 #ifndef MINICFD_B200_PEER_CUH_
 #define MINICFD_B200_PEER_CUH_
 
 namespace mcfd {
 
 constexpr int kPeerMaxNeighbours = 32, kPeerMaxRanks = 64;
+constexpr int kPeerSlots = 4, kPeerSpareSlot = 3;                // stages per state buffer, and one spare (mcfd_peer_push)
 constexpr int kPeerWords = kPeerMaxNeighbours + kPeerMaxRanks;   // delivery counts per neighbour slot, dt epochs per rank
 constexpr long long kPeerSpinLimit = 40000000;                   // about ten seconds of polling before giving up
 

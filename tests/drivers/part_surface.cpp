@@ -45,6 +45,9 @@ int main() {
     for (auto const &face : part.GetBoundaryFaces(name)) { area += face.area(); cx += face.center()[0] * face.area(); (void)face.holder().id(); }
     std::printf("section %s %zu %.17g %.17g\n", name, part.GetBoundaryFaces(name).size(), area, cx / area);
   }
+  auto l1 = part.MeasureL1Error([](Part::Global const &x, double t) {   // part.hpp:1023-1037
+    Part::Value v; v[0] = 1 + x[0] + 0.5; v[1] = x[1]; v[2] = x[2] - t; v[3] = 0; v[4] = 3 + x[0] * x[1]; return v; }, 0.25);
+  std::printf("l1 %.17g %.17g %.17g %.17g %.17g\n", l1[0], l1[1], l1[2], l1[3], l1[4]);
   // Gather -> change on the host -> Scatter -> the column shows it (part.hpp:1052-1069)
   part.GatherSolutions();
   std::printf("coeff %.17g %.17g\n", part.GetLocalCells()[3].coeff()[0], part.cell_data()[part.GetCellDataOffset(3)]);

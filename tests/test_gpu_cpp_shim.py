@@ -529,7 +529,57 @@ def test_part_surface(tmp_path):
     assert int(sections["Right"][0]) == 6 and abs(float(sections["Right"][2]) - 3.5) < 1e-13
     assert int(sections["Top"][0]) == 8 and abs(float(sections["Top"][1]) - 3.5 * 3) < 1e-13
     assert int(sections["Front"][0]) == 12 and abs(float(sections["Front"][1]) - 3.5 * 1.5) < 1e-13
+    l1 = [float(v) for v in [l for l in lines if l.startswith("l1 ")][0].split()[1:]]
+    volume = 3.5 * 3 * 1.5
+    np.testing.assert_allclose(l1, [0.5 * volume, 0, 0.25 * volume, 0, 0], rtol=1e-13, atol=1e-13)
     a, b = [float(v) for v in [l for l in lines if l.startswith("coeff ")][0].split()[1:]]
     assert a == b
     s = [float(v) for v in [l for l in lines if l.startswith("scattered ")][0].split()[1:]]
     assert s[0] == 2 * a
+
+
+def test_sod_driver_with_weno_limiter_one_process_per_part(tmp_path):
+    """-DLIMITER on two parts, one process each: mini::limiter::Reconstruct's order — share the unlimited coefficients,
+    limit the inner cells, receive, limit the inter cells (limiter/reconstruct.hpp:21-54) — and the residuals' own
+    exchange of the limited ones, all behind Part::Share/UpdateGhostCellCoeffs.  The reference's answer depends on the
+    partition; it is run on the same two parts."""
+    if not refapi.available(2):
+        pytest.skip("needs oracle/_ref (the limiter on several parts)")
+    exe = tmp_path / "shock_tube"
+    subprocess.check_call(["g++", "-DUSE_HLLC", "-DLIMITER", "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"), "-I", NOMPI,
+                           os.path.join(ROOT, "demo", "euler", "shock_tube.cpp"), "-o", str(exe),
+                           "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200", "-lrt",
+                           "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")])
+    out = tmp_path / "column.bin"
+    n_steps, world = 6, 2
+    _run_ranks(exe, [str(n_steps), str(out)], world, tmp_path)
+    m = meshmod.box(50, 2, 3, hi=(5.0, 0.2, 0.3))
+    parts = meshmod.block_partition(m, world, 1, 1)
+    left = np.array([1.0, 0, 0, 0, 1.0 / 0.4]); right = np.array([0.125, 0, 0, 0, 0.1 / 0.4])
+    r = refapi.Ref(m, degree=2, scheme=refapi.FR_WENO_LAZY, riemann=1, cell_parts=parts, n_parts=world, weno=(0.001, 1e-6))
+    def ic(tag, xyz, t, out_, user):
+        v = left if xyz[0] < 2.5 else right
+        for k in range(5):
+            out_[k] = v[k]
+    r.approximate(refapi.F_CALLBACK, cb=ic)
+    r.set_bc(meshmod.XMIN, refapi.SMART, refapi.F_CONST, left)
+    r.set_bc(meshmod.XMAX, refapi.SMART, refapi.F_CONST, right)
+    for tag in (meshmod.YMIN, meshmod.YMAX, meshmod.ZMIN, meshmod.ZMAX):
+        r.set_bc(tag, refapi.WALL)
+    t = 0.0
+    for _ in range(n_steps):
+        dt = r.time_step(0.2 / 200, 3)
+        r.rk_update(3, t, dt, 1)
+        t += dt
+    scale = 0.0
+    for p in range(world):
+        raw = np.fromfile(f"{out}.{p}", dtype=np.uint8)
+        n = int(raw[:8].view(np.int64)[0])
+        ids = raw[8:8 + 8 * n].view(np.int64)
+        got = dict(zip(ids.tolist(), raw[8 + 8 * n:].view(np.float64).reshape(n, 135)))
+        ref_ids = r.cell_global_ids(p)[:r.count_local(p)]
+        ref = r.get_solution(p).reshape(-1, 135)
+        assert sorted(got) == sorted(ref_ids.tolist())
+        scale = max(scale, np.abs(ref).max())
+        err = max(np.abs(got[g] - ref[i]).max() for i, g in enumerate(ref_ids.tolist()))
+        assert err / scale < 1e-11, (p, err)      # Sod + WENO: the reference's own one-ulp drift is 7e-13 after 6 steps
