@@ -2238,5 +2238,6 @@ __global__ void RiemannKernel(int bc_kind, int n, const double *normals, const d
 
 #include "peer.cuh"
 #include "stage_lines.cuh"
+#include "stage_nodes.cuh"
 
 #endif  // MINICFD_B200_KERNELS_CUH_

@@ -2,6 +2,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -61,6 +62,8 @@ struct mcfd_ctx {
   LineTables line_tables{};                     // the node-line kernel's share of `tables`, a kernel parameter
   DevBuf<unsigned char> line_bytes;             // its byte tables once more, in device memory (staged by cp.async)
   bool use_lines = false;                       // inviscid lumped Lobatto schemes: LineStageKernel (stage_lines.cuh)
+  bool use_nodes = false;                       // ... or its persistent one-warp-per-node form (stage_nodes.cuh)
+  int sm_count = 148;
   HostMesh mesh;
   bool has_mesh = false;
   int64_t n_cells = 0, n_tiles = 0;
@@ -210,6 +213,28 @@ cudaError_t LaunchLineA(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
   kernel<<<n_blocks, S::kThreads, S::kSharedBytes, ctx->stream>>>(a, ctx->line_tables);
   return cudaGetLastError();
 }
+// the persistent one-warp-per-node kernel: one CTA per SM walks over the tiles [a.block_begin, + n_tiles)
+template <int R>
+cudaError_t LaunchNodeR(mcfd_ctx *ctx, StageArgs const &a, int n_tiles) {
+  using S = NodeShape;
+  auto kernel = NodeStageKernel<R>;
+  static DeviceFlags configured;
+  if (!configured.Here()) {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::kSharedBytes);
+    if (e != cudaSuccess) return e;
+    configured.Set();
+  }
+  kernel<<<std::min(n_tiles, ctx->sm_count), S::kThreads, S::kSharedBytes, ctx->stream>>>(a, ctx->line_tables, n_tiles);
+  return cudaGetLastError();
+}
+cudaError_t LaunchNode(mcfd_ctx *ctx, StageArgs const &a, int n_tiles) {
+  switch (ctx->cfg.riemann) {
+  case MCFD_EXACT: return LaunchNodeR<kExact>(ctx, a, n_tiles);
+  case MCFD_HLLC: return LaunchNodeR<kHllc>(ctx, a, n_tiles);
+  default: return LaunchNodeR<kAusm>(ctx, a, n_tiles);
+  }
+}
+
 // a mesh of parallelepipeds only (uniform and sheared boxes) takes the instantiation with the metric per cell
 template <int Q, int R, int CPB>
 cudaError_t LaunchLineR(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
@@ -369,6 +394,8 @@ int LaunchStage(mcfd_ctx *ctx, const double *u_in, const double *u0, double *u_o
   } else if (ctx->cfg.diffusion != MCFD_INVISCID) {
     e = (ctx->q == 3) ? LaunchStageViscous<3, kP2ViscousCells, kP2ViscousWarps>(ctx, a, n_blocks)
                       : LaunchStageViscous<4, kP3ViscousCells, kP3ViscousWarps>(ctx, a, n_blocks);
+  } else if (ctx->use_nodes) {
+    e = LaunchNode(ctx, a, n_blocks);
   } else if (ctx->use_lines) {
     e = LaunchLine<3, kLineP2Cells>(ctx, a, n_blocks);   // degree 3 stays on the slot kernel (use_lines)
   } else {
@@ -523,7 +550,10 @@ int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
   ctx->tables = BuildTables(config->degree, config->scheme, ctx->n_warps, kTile / ctx->cpb, config->fr_c_next);
   ctx->use_lines = !viscous && ctx->q == 3 && (config->scheme == MCFD_FR_LOBATTO || config->scheme == MCFD_DG_LOBATTO);
   if (ctx->use_lines) {
-    ctx->cpb = (ctx->q == 3) ? kLineP2Cells : kLineP3Cells;
+    const char *which = std::getenv("MCFD_STAGE_KERNEL");   // "lines" | "nodes": A/B runs; the default is set here
+    ctx->use_nodes = which ? std::string(which) == "nodes" : MCFD_DEFAULT_NODE_KERNEL;
+    cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, ctx->device);
+    ctx->cpb = ctx->use_nodes ? kTile : ((ctx->q == 3) ? kLineP2Cells : kLineP3Cells);
     ctx->n_warps = (ctx->q == 3) ? LineShape<3, kLineP2Cells>::NW : LineShape<4, kLineP3Cells>::NW;
     ctx->line_tables = MakeLineTables(ctx->tables, ctx->q, kTile / ctx->cpb);
     const std::vector<unsigned char> bytes = LineTableBytes(ctx->line_tables, ctx->q);

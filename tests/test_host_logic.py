@@ -360,3 +360,27 @@ def test_nompi_allreduce_between_processes(tmp_path, world):
     for r, p in enumerate(procs):
         out = p.communicate(timeout=120)[0]
         assert p.returncode == 0 and f"rank {r} of {world} ok" in out, out
+
+
+@pytest.mark.parametrize("name,degree,scheme,riemann", [c for c in cases.GOLDEN_CASES if c[1] == 2 and c[2] in (0, 1)])
+def test_node_kernel_source_on_host_matches_golden(name, degree, scheme, riemann):
+    """stage_nodes.cuh (one warp per node, persistent; p = 2 lumped Lobatto schemes), its phase functions run thread by
+    thread on the host, against the reference's golden residual and RK3 state."""
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    m = meshmod.HexMesh(nodes=g["nodes"], cells=g["cells"], bfaces=g["bfaces"], btags=g["btags"])
+    holder, hf, tags, pts = emuapi.boundary(m, degree)
+    def bvals(t):
+        out = np.zeros(pts.shape[:2] + (5,))
+        for tag, kind in cases.MIXED_BCS.items():
+            sel = tags == tag
+            out[sel] = cases.bc_function(kind)(pts[sel], t)
+        return out
+    u = g["u"]
+    kw = dict(tag_kinds=cases.MIXED_BCS, line_cells=1)
+    res = emuapi.stage(m, degree, scheme, riemann, u, bvals=bvals(cases.GOLDEN_T), **kw)
+    assert relerr(res, g["residual"]) < 1e-12
+    dt = cases.GOLDEN_DT
+    u1 = emuapi.stage(m, degree, scheme, riemann, u, bvals=bvals(0.0), mode=1, dt=dt, **kw)
+    u2 = emuapi.stage(m, degree, scheme, riemann, u1, bvals=bvals(dt), column_u0=u, mode=2, dt=dt, **kw)
+    u3 = emuapi.stage(m, degree, scheme, riemann, u2, bvals=bvals(dt / 2), column_u0=u, mode=3, dt=dt, **kw)
+    assert relerr(u3, g["u_rk3"]) < 1e-12
