@@ -214,10 +214,10 @@ cudaError_t LaunchLineA(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) {
   return cudaGetLastError();
 }
 // the persistent one-warp-per-node kernel: one CTA per SM walks over the tiles [a.block_begin, + n_tiles)
-template <int R>
-cudaError_t LaunchNodeR(mcfd_ctx *ctx, StageArgs const &a, int n_tiles) {
+template <int R, bool kAffine>
+cudaError_t LaunchNodeA(mcfd_ctx *ctx, StageArgs const &a, int n_tiles) {
   using S = NodeShape;
-  auto kernel = NodeStageKernel<R>;
+  auto kernel = NodeStageKernel<R, kAffine>;
   static DeviceFlags configured;
   if (!configured.Here()) {
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::kSharedBytes);
@@ -226,6 +226,10 @@ cudaError_t LaunchNodeR(mcfd_ctx *ctx, StageArgs const &a, int n_tiles) {
   }
   kernel<<<std::min(n_tiles, ctx->sm_count), S::kThreads, S::kSharedBytes, ctx->stream>>>(a, ctx->line_tables, n_tiles);
   return cudaGetLastError();
+}
+template <int R>
+cudaError_t LaunchNodeR(mcfd_ctx *ctx, StageArgs const &a, int n_tiles) {
+  return ctx->mesh.all_affine ? LaunchNodeA<R, true>(ctx, a, n_tiles) : LaunchNodeA<R, false>(ctx, a, n_tiles);
 }
 cudaError_t LaunchNode(mcfd_ctx *ctx, StageArgs const &a, int n_tiles) {
   switch (ctx->cfg.riemann) {

@@ -138,6 +138,7 @@ struct NodeRegs {
 };
 
 // ---- phase A: primitive state, metric, F^_d = F(u) . (column d of J*) for d = xi, eta, zeta -> shared memory ----
+template <bool kAffine>
 MCFD_HD void NodePhaseA(const StageArgs &p, const LineTables &tab, const NodeThread &g, NodeRegs *t) {
   using S = NodeShape;
 #pragma unroll
@@ -145,11 +146,17 @@ MCFD_HD void NodePhaseA(const StageArgs &p, const LineTables &tab, const NodeThr
   bool ok;
   t->q = ConsToPrimFlat(t->u, &ok);
   if (!ok) t->q = ConsToPrimA(t->u);             // clipped or vacuum state
-  const LineJacobian J = ComputeLineJacobian(g.sG + g.lane, kTile, tab.xi[g.i], tab.xi[g.j]);
+  // a mesh of parallelepipeds (kAffine): the rows of J are c1, c2, c3 everywhere in the cell — what the general
+  // expressions give when c4..c7 vanish, bit for bit
+  const LineJacobian J = kAffine ? AffineLineJacobian(g.sG + g.lane, kTile)
+                                 : ComputeLineJacobian(g.sG + g.lane, kTile, tab.xi[g.i], tab.xi[g.j]);
   const double z = tab.xi[g.k];
   double r0[3], r1[3], s[3], f[5];
 #pragma unroll
-  for (int x = 0; x < 3; ++x) { r0[x] = fma(z, J.B0[x], J.A0[x]); r1[x] = fma(z, J.B1[x], J.A1[x]); }
+  for (int x = 0; x < 3; ++x) {
+    r0[x] = kAffine ? J.A0[x] : fma(z, J.B0[x], J.A0[x]);
+    r1[x] = kAffine ? J.A1[x] : fma(z, J.B1[x], J.A1[x]);
+  }
   double *dst = g.sF + g.n * 15 * kTile + g.lane;
   Cross(r1, J.R2, s);
   t->inv_det = RcpC(r0[0] * s[0] + r0[1] * s[1] + r0[2] * s[2]);   // fr/general.hpp:256-266; dg/lobatto.hpp:143-158
@@ -251,10 +258,16 @@ MCFD_NOINLINE void NodePointRare(const StageArgs &p, const LineTables &tab, int 
 
 // rows of the Jacobian at the node that the normal of its dd-faces needs (column dd of J* = the cross product of the
 // other two rows; the same FMA nesting as ComputeLineJacobian), straight from the tile's geometry rows
+template <bool kAffine>
 MCFD_HD void NodeNormal(const double *g, double x, double e, double z, int dd, double *nr) {
   double ra[3], rb[3];
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
+    if (kAffine) {   // rows c1, c2, c3: only the two the cross product takes are read
+      ra[k] = g[((dd == 0 ? 3 : (dd == 1 ? 6 : 0)) + k) * kTile];
+      rb[k] = g[((dd == 0 ? 6 : (dd == 1 ? 0 : 3)) + k) * kTile];
+      continue;
+    }
     const double c4 = g[(9 + k) * kTile], c6 = g[(15 + k) * kTile], c7 = g[(18 + k) * kTile];
     const double b1 = fma(x, c7, g[(12 + k) * kTile]);
     const double r0 = fma(z, fma(e, c7, c6), fma(e, c4, g[(0 + k) * kTile]));
@@ -269,7 +282,7 @@ MCFD_HD void NodeNormal(const double *g, double x, double e, double z, int dd, d
 // ---- phase C: the node's face points (0..3).  Everything a point needs is the thread's own: its primitive state in
 // registers, the neighbour's state in its slot of sN, the metric from the tile's geometry rows.  The lifted term
 // goes straight into the residual in registers (fr/general.hpp:296-315; dg/lobatto.hpp:171-191).
-template <int kRiemann>
+template <int kRiemann, bool kAffine>
 MCFD_HD void NodePhaseC(const StageArgs &p, const LineTables &tab, const NodeThread &g, double *smem, NodeRegs *t) {
   using S = NodeShape;
   if (!g.active) return;
@@ -279,7 +292,7 @@ MCFD_HD void NodePhaseC(const StageArgs &p, const LineTables &tab, const NodeThr
     if (f < 0) continue;                       // warp uniform
     const int q = tab.node_q[g.n][dd];
     double nr[3];
-    NodeNormal(g.sG + g.lane, tab.xi[g.i], tab.xi[g.j], tab.xi[g.k], dd, nr);
+    NodeNormal<kAffine>(g.sG + g.lane, tab.xi[g.i], tab.xi[g.j], tab.xi[g.k], dd, nr);
     const double sgn = (f == 2 || f == 3 || f == 5) ? 1.0 : -1.0;
     const double n2 = nr[0] * nr[0] + nr[1] * nr[1] + nr[2] * nr[2];
     const double inv_area = RsqrtC(n2);
@@ -385,7 +398,7 @@ __device__ __forceinline__ void NodeProduce(const StageArgs &p, int tile, int bu
   BulkCopy(bytes + S::kOffCode + buf * S::kCodeBytes, p.code + (size_t)tile * 6 * kTile, S::kCodeBytes, bar);
 }
 
-template <int kRiemann>
+template <int kRiemann, bool kAffine>
 __global__ void __launch_bounds__(NodeShape::kThreads, 1)
 NodeStageKernel(const __grid_constant__ StageArgs p, const __grid_constant__ LineTables tab, int n_tiles) {
   using S = NodeShape;
@@ -421,14 +434,14 @@ NodeStageKernel(const __grid_constant__ StageArgs p, const __grid_constant__ Lin
       for (int c = 0; c < 5; ++c) MCFD_PREFETCH_L2(u0 + c * kTile);
     }
     NodeRegs r;
-    NodePhaseA(p, tab, g, &r);
+    NodePhaseA<kAffine>(p, tab, g, &r);
     __syncthreads();                       // F^ complete; the own-state buffer has been read
     if (producer && more) NodeProduce(p, p.block_begin + t + gridDim.x, buf ^ 1, smem, &waited);
     NodePhaseB(tab, g, &r);
     __syncthreads();                       // F^ may be overwritten by the next tile
     NodeStash(g, r);
     asm volatile("cp.async.wait_group 0;" ::: "memory");   // my gathers for this tile
-    NodePhaseC<kRiemann>(p, tab, g, smem, &r);
+    NodePhaseC<kRiemann, kAffine>(p, tab, g, smem, &r);
     if (more) {                            // my slots of sN are free: the next tile's neighbours
       MbarWait(bytes + S::kOffBar + 8 * (buf ^ 1), ((it + 1) >> 1) & 1);
       const NodeThread gn(p, tid, p.block_begin + t + gridDim.x, buf ^ 1, smem);
@@ -440,7 +453,7 @@ NodeStageKernel(const __grid_constant__ StageArgs p, const __grid_constant__ Lin
 }
 #else
 // the same tile by tile on the host (tests/host_emulation): every thread of a phase before the next phase
-template <int kRiemann>
+template <int kRiemann, bool kAffine>
 void RunNodeStageTileOnHost(const StageArgs &p, const LineTables &tab, int tile, double *smem) {
   using S = NodeShape;
   unsigned char *bytes = reinterpret_cast<unsigned char *>(smem + S::kDoubles);
@@ -455,13 +468,13 @@ void RunNodeStageTileOnHost(const StageArgs &p, const LineTables &tab, int tile,
   for (int t = 0; t < S::kThreads; ++t) {
     const NodeThread g(p, t, tile, 0, smem);
     NodeGather(p, tab, g);
-    NodePhaseA(p, tab, g, &regs[t]);
+    NodePhaseA<kAffine>(p, tab, g, &regs[t]);
   }
   for (int t = 0; t < S::kThreads; ++t) NodePhaseB(tab, NodeThread(p, t, tile, 0, smem), &regs[t]);
   for (int t = 0; t < S::kThreads; ++t) {
     const NodeThread g(p, t, tile, 0, smem);
     NodeStash(g, regs[t]);
-    NodePhaseC<kRiemann>(p, tab, g, smem, &regs[t]);
+    NodePhaseC<kRiemann, kAffine>(p, tab, g, smem, &regs[t]);
     NodePhaseD(p, g);
   }
 }

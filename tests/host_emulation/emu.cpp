@@ -52,7 +52,8 @@ void RunLineStage(int riemann, StageArgs a, int64_t n_local, bool affine) {
 }
 
 // the persistent one-warp-per-node kernel (stage_nodes.cuh), tile by tile
-void RunNodeStage(int riemann, StageArgs a, int64_t n_local) {
+template <bool kAffine>
+void RunNodeStageA(int riemann, StageArgs a, int64_t n_local) {
   using S = NodeShape;
   std::vector<double> smem(S::kSharedBytes / sizeof(double) + 1);
   const LineTables tab = MakeLineTables(c_tab, 3, 1);
@@ -60,10 +61,15 @@ void RunNodeStage(int riemann, StageArgs a, int64_t n_local) {
   a.line_bytes = bytes.data();
   const int n_tiles = (int)((n_local + kTile - 1) / kTile);
   for (int t = 0; t < n_tiles; ++t) {
-    if (riemann == 0) RunNodeStageTileOnHost<kExact>(a, tab, t, smem.data());
-    else if (riemann == 1) RunNodeStageTileOnHost<kHllc>(a, tab, t, smem.data());
-    else RunNodeStageTileOnHost<kAusm>(a, tab, t, smem.data());
+    if (riemann == 0) RunNodeStageTileOnHost<kExact, kAffine>(a, tab, t, smem.data());
+    else if (riemann == 1) RunNodeStageTileOnHost<kHllc, kAffine>(a, tab, t, smem.data());
+    else RunNodeStageTileOnHost<kAusm, kAffine>(a, tab, t, smem.data());
   }
+}
+
+void RunNodeStage(int riemann, StageArgs a, int64_t n_local, bool affine) {
+  if (affine) RunNodeStageA<true>(riemann, a, n_local);
+  else RunNodeStageA<false>(riemann, a, n_local);
 }
 
 template <int Q, int CPB, int NW>
@@ -147,7 +153,7 @@ int emu_stage(int degree, int scheme, int riemann, int64_t n_nodes, const double
   }
   int n_blocks = (int)((n_local + cpb - 1) / cpb);
   const bool lines = !viscous && scheme != 2 && line_cells != 0;   // what LaunchStage of the library picks
-  if (lines && q == 3 && line_cells == 1) RunNodeStage(riemann, a, n_local);
+  if (lines && q == 3 && line_cells == 1) RunNodeStage(riemann, a, n_local, mesh.all_affine);
   else if (lines && q == 3 && line_cells == 16) RunLineStage<3, 16>(riemann, a, n_local, mesh.all_affine);
   else if (lines && q == 3) RunLineStage<3, 32>(riemann, a, n_local, mesh.all_affine);
   else if (lines && line_cells == 32) RunLineStage<4, 32>(riemann, a, n_local, mesh.all_affine);
