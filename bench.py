@@ -45,13 +45,16 @@ def stage_kernel_name(args):
     if args.scheme == "dgm":
         return f"mcfd::DgmStageKernel (degree {args.degree})"
     if args.viscous is None and not args.energy_viscosity and q == 3:
+        if getattr(args, "stage_kernel", None) == "nodes" or (args.stage_kernel is None and os.environ.get("MCFD_STAGE_KERNEL") == "nodes"):
+            return f"mcfd::NodeStageKernel<{args.riemann}> (persistent, one warp per node)"
         return f"mcfd::LineStageKernel<{q}, {args.riemann}, 16 cells per CTA>"
     return f"mcfd::StageKernel<{q}, {args.riemann}>"
 
 
 def traffic_shape(args, world):
     """Key of profiles/stage_kernel_traffic.json: the configuration whose stage kernel the ncu capture profiled."""
-    plain = args.viscous is None and not args.limiter and not args.energy_viscosity and args.warp == 0.0
+    plain = (args.viscous is None and not args.limiter and not args.energy_viscosity and args.warp == 0.0
+             and stage_kernel_name(args).startswith("mcfd::LineStageKernel"))
     return f"{args.scheme} p{args.degree} {args.riemann} {args.cells}^3 cells per GPU {'inviscid' if plain else 'other'} n{world}"
 
 
@@ -86,6 +89,9 @@ def parse():
                          "inviscid nodal schemes) or pack -> NCCL send/recv -> unpack issued from Python")
     ap.add_argument("--warp", type=float, default=0.0,
                     help="displace the interior mesh nodes by this fraction of h (non-affine cells: the general metric path)")
+    ap.add_argument("--stage-kernel", default=None, choices=["lines", "nodes"],
+                    help="p = 2 inviscid nodal schemes: the node-line kernel (default) or the persistent one-warp-per-node "
+                         "kernel (csrc/stage_nodes.cuh); sets MCFD_STAGE_KERNEL for the contexts of this run")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of replaying a CUDA graph")
     return ap.parse_args()
 
@@ -258,6 +264,7 @@ def config_dict(args, n_gpus, dims, part):
                         (f", interior nodes displaced by {args.warp} h" if getattr(args, "warp", 0.0) else ""),
             "cells_per_gpu": args.cells ** 3, "dof_per_gpu": args.cells ** 3 * 5 * (args.degree + 1) ** 3,
             "step": "GetTimeStep + RungeKutta<3>::Update (3 stages)", "parallelism": f"domain decomposition {part}",
+            "stage_kernel": stage_kernel_name(args),
             "l2_policy": l2_policy(args)}
 
 
@@ -322,6 +329,7 @@ def algorithmic_bytes(args):
 
 
 FEATURES = [   # name, overrides of the headline arguments
+    ("node_kernel", {"stage_kernel": "nodes"}),
     ("viscous", {"viscous": 0.01}),
     ("limiter", {"limiter": True}),
     ("energy_viscosity", {"energy_viscosity": True}),
@@ -348,7 +356,7 @@ def ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     line = measure(args, world, rank, local_rank)
     plain = (args.viscous is None and not args.limiter and not args.energy_viscosity and args.scheme == "fr"
-             and args.degree == 2 and args.warp == 0.0)
+             and args.degree == 2 and args.warp == 0.0 and args.stage_kernel is None)
     if plain and world == 1 and not args.no_features:
         # the other configurations of the path, briefly, each with its own algorithmic-bytes roofline.  One GPU only:
         # under torchrun every one of them is its own run (e.g. `--gpus 8 --degree 3 --cells 32` for BASELINE
@@ -388,6 +396,9 @@ def measure(args, world, rank, local_rank, nested=False):
     from minicfd_b200.part import Part
     from minicfd_b200.spatial import RungeKutta, Spatial
 
+    env_before = os.environ.get("MCFD_STAGE_KERNEL")
+    if args.stage_kernel is not None:          # read by mcfd_create, i.e. when the Spatial below is built
+        os.environ["MCFD_STAGE_KERNEL"] = args.stage_kernel
     px, py, pz = meshmod.factor3(world)
     n = args.cells
     dims = (n * px, n * py, n * pz)
@@ -400,6 +411,11 @@ def measure(args, world, rank, local_rank, nested=False):
     sp = Spatial(part, scheme=scheme, degree=args.degree, riemann=RIEMANN[args.riemann], device=local_rank,
                  comm=comm, diffusion=capi.CELL_VISCOSITY_DDG if args.energy_viscosity else
                  (capi.INVISCID if args.viscous is None else capi.NAVIER_STOKES_DDG))
+    if args.stage_kernel is not None:
+        if env_before is None:
+            del os.environ["MCFD_STAGE_KERNEL"]
+        else:
+            os.environ["MCFD_STAGE_KERNEL"] = env_before
     if args.energy_viscosity:
         sp.SetDiffusion(2.0, 1.0 / 12, 0.0, 0.708)
         sp.EnableEnergyBasedViscosity()

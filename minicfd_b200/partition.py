@@ -245,3 +245,17 @@ def part_from_partition(info: PartitionInfo, sm: ShuffledMesh, rank: int) -> Par
     p.bfaces = np.concatenate(quads) if quads else np.zeros((0, 4), dtype=np.int64)
     p.btags = np.concatenate(tags) if tags else np.zeros((0,), dtype=np.int32)
     return p
+
+
+def partition_and_shuffle(case_dir: str, mesh: HexMesh, n_parts: int, cell_parts=None) -> ShuffledMesh:
+    """`Shuffler::PartitionAndShuffle` (shuffler.hpp:510-546) without its file I/O: dual graph of the cells
+    (METIS_MeshToDual, n_common = 3), the cells' parts, the nodes' parts (metis::GetNodeParts), the reordering, and
+    the per-part index files under `<case_dir>/partition/`.  METIS_PartGraphKway itself is not on this image
+    (DESIGN.md section 6): `cell_parts` comes from the caller, or, failing that, consecutive runs of cells in mesh
+    order — a valid input for everything downstream, not METIS's answer."""
+    if cell_parts is None:
+        cell_parts = (np.arange(mesh.n_cells) * n_parts // max(mesh.n_cells, 1)).astype(np.int32)
+    pairs = dual_graph(mesh)
+    sm = shuffle(mesh, cell_parts, n_parts)
+    write_partition_info(case_dir, mesh, cell_parts, sm, pairs=pairs)
+    return sm

@@ -58,6 +58,17 @@ def test_part_from_the_file_equals_part_from_the_whole_mesh(tmp_path, n_parts):
         assert all(sm.node_metis[i_node - 1] == node for (_, node, _, i_node) in info.adj_nodes)
 
 
+def test_partition_and_shuffle_writes_one_file_per_part(tmp_path):
+    m = meshmod.scramble(meshmod.box(4, 4, 2), seed=3)
+    sm = partition.partition_and_shuffle(str(tmp_path), m, 4)
+    assert sorted(os.listdir(tmp_path / "partition")) == ["0.txt", "1.txt", "2.txt", "3.txt"]
+    n_local = 0
+    for r in range(4):
+        p = partition.part_from_partition(partition.read_partition_info(str(tmp_path / "partition" / f"{r}.txt")), sm, r)
+        n_local += p.n_local
+    assert n_local == m.n_cells
+
+
 @pytest.mark.gpu
 def test_parts_from_the_files_advance_like_the_whole_mesh(tmp_path):
     """Three parts built from their partition files, advanced on one GPU with the device-side ghost exchange, against
