@@ -117,6 +117,7 @@ def test_driver_writes_frames_like_the_reference(tmp_path):
     import test_gpu_cpp_shim as shim
     exe = tmp_path / "shock_tube_viscosity"
     subprocess.check_call(["g++", "-DUSE_HLLC", "-DVISCOSITY", "-std=c++20", "-O2", "-I", os.path.join(ROOT, "include"),
+                           "-I", os.path.join(ROOT, "include", "mini", "b200", "nompi"),
                            os.path.join(ROOT, "demo", "euler", "shock_tube.cpp"), "-o", str(exe),
                            "-L", os.path.join(ROOT, "minicfd_b200"), "-lminicfd_b200",
                            "-Wl,-rpath," + os.path.join(ROOT, "minicfd_b200")])
