@@ -45,16 +45,18 @@ def stage_kernel_name(args):
     if args.scheme == "dgm":
         return f"mcfd::DgmStageKernel (degree {args.degree})"
     if args.viscous is None and not args.energy_viscosity and q == 3:
-        if getattr(args, "stage_kernel", None) == "nodes" or (args.stage_kernel is None and os.environ.get("MCFD_STAGE_KERNEL") == "nodes"):
-            return f"mcfd::NodeStageKernel<{args.riemann}> (persistent, one warp per node)"
-        return f"mcfd::LineStageKernel<{q}, {args.riemann}, 16 cells per CTA>"
+        # the library's choice (mcfd_set_mesh): the node kernel on meshes of parallelepipeds, unless told otherwise
+        which = getattr(args, "stage_kernel", None) or os.environ.get("MCFD_STAGE_KERNEL") or ("nodes" if args.warp == 0.0 else "lines")
+        if which == "nodes":
+            return f"mcfd::NodeStageKernel<{args.riemann}, {'affine' if args.warp == 0.0 else 'general'}> (persistent, one warp per node)"
+        return f"mcfd::LineStageKernel<{q}, {args.riemann}, 16 cells per CTA, {'affine' if args.warp == 0.0 else 'general'}>"
     return f"mcfd::StageKernel<{q}, {args.riemann}>"
 
 
 def traffic_shape(args, world):
     """Key of profiles/stage_kernel_traffic.json: the configuration whose stage kernel the ncu capture profiled."""
     plain = (args.viscous is None and not args.limiter and not args.energy_viscosity and args.warp == 0.0
-             and stage_kernel_name(args).startswith("mcfd::LineStageKernel"))
+             and stage_kernel_name(args).startswith("mcfd::NodeStageKernel"))
     return f"{args.scheme} p{args.degree} {args.riemann} {args.cells}^3 cells per GPU {'inviscid' if plain else 'other'} n{world}"
 
 
@@ -90,8 +92,9 @@ def parse():
     ap.add_argument("--warp", type=float, default=0.0,
                     help="displace the interior mesh nodes by this fraction of h (non-affine cells: the general metric path)")
     ap.add_argument("--stage-kernel", default=None, choices=["lines", "nodes"],
-                    help="p = 2 inviscid nodal schemes: the node-line kernel (default) or the persistent one-warp-per-node "
-                         "kernel (csrc/stage_nodes.cuh); sets MCFD_STAGE_KERNEL for the contexts of this run")
+                    help="p = 2 inviscid nodal schemes: the node-line kernel or the persistent one-warp-per-node kernel "
+                         "(csrc/stage_nodes.cuh); sets MCFD_STAGE_KERNEL for the contexts of this run.  Default: the "
+                         "library's choice (nodes on meshes of parallelepipeds, lines elsewhere)")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of replaying a CUDA graph")
     return ap.parse_args()
 
@@ -329,7 +332,7 @@ def algorithmic_bytes(args):
 
 
 FEATURES = [   # name, overrides of the headline arguments
-    ("node_kernel", {"stage_kernel": "nodes"}),
+    ("line_kernel", {"stage_kernel": "lines"}),
     ("viscous", {"viscous": 0.01}),
     ("limiter", {"limiter": True}),
     ("energy_viscosity", {"energy_viscosity": True}),

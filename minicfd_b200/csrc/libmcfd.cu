@@ -63,6 +63,7 @@ struct mcfd_ctx {
   DevBuf<unsigned char> line_bytes;             // its byte tables once more, in device memory (staged by cp.async)
   bool use_lines = false;                       // inviscid lumped Lobatto schemes: LineStageKernel (stage_lines.cuh)
   bool use_nodes = false;                       // ... or its persistent one-warp-per-node form (stage_nodes.cuh)
+  bool stage_kernel_forced = false;             // MCFD_STAGE_KERNEL chose; else mcfd_set_mesh does (all_affine)
   int sm_count = 148;
   HostMesh mesh;
   bool has_mesh = false;
@@ -554,8 +555,11 @@ int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
   ctx->tables = BuildTables(config->degree, config->scheme, ctx->n_warps, kTile / ctx->cpb, config->fr_c_next);
   ctx->use_lines = !viscous && ctx->q == 3 && (config->scheme == MCFD_FR_LOBATTO || config->scheme == MCFD_DG_LOBATTO);
   if (ctx->use_lines) {
-    const char *which = std::getenv("MCFD_STAGE_KERNEL");   // "lines" | "nodes": A/B runs; the default is set here
-    ctx->use_nodes = which ? std::string(which) == "nodes" : MCFD_DEFAULT_NODE_KERNEL;
+    // "lines" | "nodes" for A/B runs; without it mcfd_set_mesh decides: the node kernel where every cell is a
+    // parallelepiped (146 against 155 us per stage on the benchmark box), the node-line kernel elsewhere (164 : 166)
+    const char *which = std::getenv("MCFD_STAGE_KERNEL");
+    ctx->stage_kernel_forced = which != nullptr;
+    ctx->use_nodes = which ? std::string(which) == "nodes" : false;
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, ctx->device);
     ctx->cpb = ctx->use_nodes ? kTile : ((ctx->q == 3) ? kLineP2Cells : kLineP3Cells);
     ctx->n_warps = (ctx->q == 3) ? LineShape<3, kLineP2Cells>::NW : LineShape<4, kLineP3Cells>::NW;
@@ -666,6 +670,10 @@ int mcfd_set_mesh(mcfd_ctx *ctx, int64_t n_nodes, const double *xyz, int64_t n_l
   MCFD_CUDA(ctx, ctx->bvals.Alloc(std::max<size_t>(nb, 1) * ctx->q * ctx->q * 5));
   MCFD_CUDA(ctx, cudaMemset(ctx->bvals.p, 0, ctx->bvals.n * sizeof(double)));
   if (nb) MCFD_CUDA(ctx, cudaMemcpy(ctx->bkind.p, ctx->bkind_host.data(), nb, cudaMemcpyHostToDevice));
+  if (ctx->use_lines && !ctx->stage_kernel_forced) {
+    ctx->use_nodes = ctx->mesh.all_affine;
+    ctx->cpb = ctx->use_nodes ? kTile : kLineP2Cells;
+  }
   // CTA blocks that contain only inner cells: cells are ordered inner first (part.hpp:746-767);
   // a local cell is "inter" when one of its neighbours is a ghost.
   int64_t first_inter = n_local;

@@ -20,10 +20,6 @@
 #ifndef MINICFD_B200_STAGE_NODES_CUH_
 #define MINICFD_B200_STAGE_NODES_CUH_
 
-#ifndef MCFD_DEFAULT_NODE_KERNEL
-#define MCFD_DEFAULT_NODE_KERNEL false   // which of the two p = 2 kernels a context takes unless MCFD_STAGE_KERNEL says
-#endif
-
 namespace mcfd {
 
 struct NodeShape {

@@ -261,7 +261,7 @@ struct HostMesh {
   std::vector<double> frames;        // [cell][6][9] normal frame (normal, tangent, bitangent) of that face at its
                                      // quadrature point 0, as rotated::Euler::Rotate receives it (fem.hpp:103-106)
   std::vector<double> length, volume;  // local cells
-  bool all_affine = false;             // every local cell is a parallelepiped: c4..c7 = 0 exactly, J constant per cell
+  bool all_affine = false;             // every local cell is a parallelepiped (c4..c7 below 64 ulp of c1..c3): J constant per cell
   // optional: the cells' ids in the whole mesh.  The reference decides holder / sharer of a face between two
   // local cells by those (holder = smaller id, mesh/shuffler.hpp:417-420), not by the part-local numbering.
   std::vector<int64_t> global_ids;
@@ -537,7 +537,12 @@ struct HostMesh {
         }
       }
       if (c >= nl) continue;
-      for (int k = 9; k < kGeomRows; ++k) if (coef[c * kGeomRows + k] != 0.0) all_affine = false;
+      {   // a parallelepiped up to the rounding of its vertex coordinates: the bilinear and trilinear terms vanish
+        double lin = 0, rest = 0;
+        for (int k = 0; k < 9; ++k) lin = std::max(lin, std::fabs(coef[c * kGeomRows + k]));
+        for (int k = 9; k < kGeomRows; ++k) rest = std::max(rest, std::fabs(coef[c * kGeomRows + k]));
+        if (rest > 64 * 2.220446049250313e-16 * lin) all_affine = false;
+      }
       double vol = 0;
       for (int i = 0; i < q; ++i) for (int j = 0; j < q; ++j) for (int k = 0; k < q; ++k) {
         double r[3][3];
