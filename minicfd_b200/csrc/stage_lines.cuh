@@ -20,8 +20,8 @@
 //     into the send stage (peer.cuh);
 //   * the Jacobian rows of the trilinear map split into a part that is constant along the line and a part
 //     linear in zeta, so the metric of a node costs 6 FMA + 3 cross products, and the face normals of a line
-//     come from the same pieces; a mesh whose cells are all parallelepipeds takes an instantiation with one
-//     metric per cell (kAffine; bit-identical results, measured: no faster — the kernel is latency bound);
+//     come from the same pieces; a mesh whose cells are all parallelepipeds (up to rounding) takes an instantiation
+//     with one metric per cell (kAffine: 155 instead of 164 us per stage; such meshes go to stage_nodes.cuh by default);
 //   * reciprocals and square roots: one MUFU seed + one cubic step; HLLC with the two square roots per side
 //     merged (a_K q_K is one root) and one reciprocal per star region;
 //   * the per-degree tables travel as a kernel parameter (constant bank), the byte tables are staged in shared

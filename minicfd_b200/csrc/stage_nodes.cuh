@@ -1,4 +1,5 @@
-// stage_nodes.cuh — the inviscid stage kernel of the lumped Lobatto schemes at p = 2, "one warp per node", persistent.
+// stage_nodes.cuh — the inviscid stage kernel of the lumped Lobatto schemes at p = 2, "one warp per node", persistent:
+// what mcfd_set_mesh picks for meshes of parallelepipeds (MCFD_STAGE_KERNEL=lines|nodes overrides).
 // Included at the end of kernels.cuh, after stage_lines.cuh whose device functions (HllcFlux, ConsToPrimFlat,
 // ComputeLineJacobian, ContravariantFlux, RcpC ...) and tables (LineTables) it shares.
 //
