@@ -32,14 +32,16 @@ struct NodeShape {
   static constexpr int kOffN = kOffF + N * 15 * kTile;       // neighbour states [NP][5][32]
   static constexpr int kOffU = kOffN + NP * 5 * kTile;       // own state [F][32]
   static constexpr int kOffG = kOffU + F * kTile;            // geometry [2][21][32]
-  static constexpr int kDoubles = kOffG + 2 * kGeomRows * kTile;
+  static constexpr int kOffA = kOffG + 2 * kGeomRows * kTile;   // affine meshes: per-cell metric [2][16][32]
+  static constexpr int kAffineRows = 16;                     // columns of J* (3 x 3), 1 / length and length of each (2 x 3), 1 / det J
+  static constexpr int kDoubles = kOffA + 2 * kAffineRows * kTile;
   // then, in bytes from kDoubles * 8
   static constexpr int kNbrBytes = 6 * kTile * 4, kCodeBytes = 6 * kTile;
   static constexpr int kOffNbr = 0;                          // int [2][6][32]
   static constexpr int kOffCode = kOffNbr + 2 * kNbrBytes;   // uchar [2][6][32]
   static constexpr int kOffTab = kOffCode + 2 * kCodeBytes;  // nbr_node [6][8][FQ]
-  static constexpr int kOffBar = (kOffTab + 6 * 8 * FQ + 15) / 16 * 16;   // two mbarriers
-  static constexpr size_t kSharedBytes = (size_t)kDoubles * 8 + kOffBar + 16;
+  static constexpr int kOffBar = (kOffTab + 6 * 8 * FQ + 15) / 16 * 16;   // four mbarriers: tile data [2], affine metric [2]
+  static constexpr size_t kSharedBytes = (size_t)kDoubles * 8 + kOffBar + 32;
   static constexpr int kBulkBytes = F * kTile * 8 + kGeomRows * kTile * 8 + kNbrBytes + kCodeBytes;
 };
 
@@ -63,6 +65,9 @@ __device__ __forceinline__ void MbarWait(void *bar, int parity) {
     if (spins > (1ll << 26)) __trap();   // a copy that never lands: fail instead of hanging the device
   }
 }
+__device__ __forceinline__ void MbarArrive(void *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(SmemAddr(bar)) : "memory");
+}
 // global -> shared, `bytes` (a multiple of 16) in one piece; completion is counted on the mbarrier
 __device__ __forceinline__ void BulkCopy(void *dst_shared, const void *src, int bytes, void *bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -74,7 +79,7 @@ __device__ __forceinline__ void BulkCopy(void *dst_shared, const void *src, int 
 struct NodeThread {
   int lane, n, i, j, k, tile, cell, buf;
   bool active;
-  double *sF, *sN, *sU, *sG;
+  double *sF, *sN, *sU, *sG, *sA;
   int *sNbr;
   unsigned char *sCode, *sNbrNode;
   MCFD_HD NodeThread(const StageArgs &p, int tid, int tile_, int buf_, double *smem) {
@@ -86,6 +91,7 @@ struct NodeThread {
     active = cell < p.n_local;
     sF = smem + S::kOffF; sN = smem + S::kOffN; sU = smem + S::kOffU;
     sG = smem + S::kOffG + buf * kGeomRows * kTile;
+    sA = smem + S::kOffA + buf * S::kAffineRows * kTile;
     unsigned char *bytes = reinterpret_cast<unsigned char *>(smem + S::kDoubles);
     sNbr = reinterpret_cast<int *>(bytes + S::kOffNbr + buf * S::kNbrBytes);
     sCode = bytes + S::kOffCode + buf * S::kCodeBytes;
@@ -126,6 +132,31 @@ MCFD_HD void NodeGather(const StageArgs &p, const LineTables &tab, const NodeThr
   }
 }
 
+// A mesh of parallelepipeds: J is constant in a cell.  One warp (lanes = the cells of the tile) leaves the three
+// columns of J*, their lengths and reciprocal lengths and 1 / det J in shared memory, one tile ahead — the same
+// operations on the same numbers as every node and face point would perform (rows of J = c1, c2, c3).
+MCFD_HD void NodeAffineRows(const NodeThread &g) {
+  const double *gm = g.sG + g.lane;
+  double c[3][3], nrm[3][3];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+#pragma unroll
+    for (int x = 0; x < 3; ++x) c[r][x] = gm[(r * 3 + x) * kTile];
+  }
+  Cross(c[1], c[2], nrm[0]); Cross(c[2], c[0], nrm[1]); Cross(c[0], c[1], nrm[2]);
+  double *a = g.sA + g.lane;
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    const double n2 = nrm[d][0] * nrm[d][0] + nrm[d][1] * nrm[d][1] + nrm[d][2] * nrm[d][2];
+    const double inv_area = RsqrtC(n2);
+#pragma unroll
+    for (int x = 0; x < 3; ++x) a[(d * 5 + x) * kTile] = nrm[d][x];
+    a[(d * 5 + 3) * kTile] = inv_area;
+    a[(d * 5 + 4) * kTile] = n2 * inv_area;
+  }
+  a[15 * kTile] = RcpC(c[0][0] * nrm[0][0] + c[0][1] * nrm[0][1] + c[0][2] * nrm[0][2]);
+}
+
 // what a thread carries from phase to phase
 struct NodeRegs {
   double u[5];       // own state
@@ -143,18 +174,26 @@ MCFD_HD void NodePhaseA(const StageArgs &p, const LineTables &tab, const NodeThr
   bool ok;
   t->q = ConsToPrimFlat(t->u, &ok);
   if (!ok) t->q = ConsToPrimA(t->u);             // clipped or vacuum state
-  // a mesh of parallelepipeds (kAffine): the rows of J are c1, c2, c3 everywhere in the cell — what the general
-  // expressions give when c4..c7 vanish, bit for bit
-  const LineJacobian J = kAffine ? AffineLineJacobian(g.sG + g.lane, kTile)
-                                 : ComputeLineJacobian(g.sG + g.lane, kTile, tab.xi[g.i], tab.xi[g.j]);
-  const double z = tab.xi[g.k];
-  double r0[3], r1[3], s[3], f[5];
-#pragma unroll
-  for (int x = 0; x < 3; ++x) {
-    r0[x] = kAffine ? J.A0[x] : fma(z, J.B0[x], J.A0[x]);
-    r1[x] = kAffine ? J.A1[x] : fma(z, J.B1[x], J.A1[x]);
-  }
   double *dst = g.sF + g.n * 15 * kTile + g.lane;
+  double s[3], f[5];
+  if (kAffine) {   // the columns of J* and 1 / det J of the cell are waiting in shared memory (NodeAffineRows)
+    const double *a = g.sA + g.lane;
+    t->inv_det = a[15 * kTile];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+#pragma unroll
+      for (int x = 0; x < 3; ++x) s[x] = a[(d * 5 + x) * kTile];
+      ContravariantFlux(t->u, t->q, s, f);
+#pragma unroll
+      for (int c = 0; c < 5; ++c) dst[(d * 5 + c) * kTile] = f[c];
+    }
+    return;
+  }
+  const LineJacobian J = ComputeLineJacobian(g.sG + g.lane, kTile, tab.xi[g.i], tab.xi[g.j]);
+  const double z = tab.xi[g.k];
+  double r0[3], r1[3];
+#pragma unroll
+  for (int x = 0; x < 3; ++x) { r0[x] = fma(z, J.B0[x], J.A0[x]); r1[x] = fma(z, J.B1[x], J.A1[x]); }
   Cross(r1, J.R2, s);
   t->inv_det = RcpC(r0[0] * s[0] + r0[1] * s[1] + r0[2] * s[2]);   // fr/general.hpp:256-266; dg/lobatto.hpp:143-158
   ContravariantFlux(t->u, t->q, s, f);
@@ -255,16 +294,10 @@ MCFD_NOINLINE void NodePointRare(const StageArgs &p, const LineTables &tab, int 
 
 // rows of the Jacobian at the node that the normal of its dd-faces needs (column dd of J* = the cross product of the
 // other two rows; the same FMA nesting as ComputeLineJacobian), straight from the tile's geometry rows
-template <bool kAffine>
 MCFD_HD void NodeNormal(const double *g, double x, double e, double z, int dd, double *nr) {
   double ra[3], rb[3];
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
-    if (kAffine) {   // rows c1, c2, c3: only the two the cross product takes are read
-      ra[k] = g[((dd == 0 ? 3 : (dd == 1 ? 6 : 0)) + k) * kTile];
-      rb[k] = g[((dd == 0 ? 6 : (dd == 1 ? 0 : 3)) + k) * kTile];
-      continue;
-    }
     const double c4 = g[(9 + k) * kTile], c6 = g[(15 + k) * kTile], c7 = g[(18 + k) * kTile];
     const double b1 = fma(x, c7, g[(12 + k) * kTile]);
     const double r0 = fma(z, fma(e, c7, c6), fma(e, c4, g[(0 + k) * kTile]));
@@ -288,12 +321,19 @@ MCFD_HD void NodePhaseC(const StageArgs &p, const LineTables &tab, const NodeThr
     const int f = NodeFace(g.i, g.j, g.k, dd);
     if (f < 0) continue;                       // warp uniform
     const int q = tab.node_q[g.n][dd];
-    double nr[3];
-    NodeNormal<kAffine>(g.sG + g.lane, tab.xi[g.i], tab.xi[g.j], tab.xi[g.k], dd, nr);
+    double nr[3], inv_area, area;
     const double sgn = (f == 2 || f == 3 || f == 5) ? 1.0 : -1.0;
-    const double n2 = nr[0] * nr[0] + nr[1] * nr[1] + nr[2] * nr[2];
-    const double inv_area = RsqrtC(n2);
-    const double area = n2 * inv_area, os_ = sgn * inv_area;
+    if (kAffine) {   // the cell's column dd of J*, its length and the reciprocal wait in shared memory
+      const double *a = g.sA + dd * 5 * kTile + g.lane;
+      nr[0] = a[0]; nr[1] = a[kTile]; nr[2] = a[2 * kTile];
+      inv_area = a[3 * kTile]; area = a[4 * kTile];
+    } else {
+      NodeNormal(g.sG + g.lane, tab.xi[g.i], tab.xi[g.j], tab.xi[g.k], dd, nr);
+      const double n2 = nr[0] * nr[0] + nr[1] * nr[1] + nr[2] * nr[2];
+      inv_area = RsqrtC(n2);
+      area = n2 * inv_area;
+    }
+    const double os_ = sgn * inv_area;
     const double ox = os_ * nr[0], oy = os_ * nr[1], oz = os_ * nr[2];   // own outward unit normal
     double fl[5], scale;
     if (kRiemann == kHllc) {
@@ -408,6 +448,8 @@ NodeStageKernel(const __grid_constant__ StageArgs p, const __grid_constant__ Lin
   if (producer) {
     MbarInit(bytes + S::kOffBar, 1);
     MbarInit(bytes + S::kOffBar + 8, 1);
+    MbarInit(bytes + S::kOffBar + 16, 32);   // the affine metric of a tile: the 32 lanes of the warp that computes it
+    MbarInit(bytes + S::kOffBar + 24, 32);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -419,12 +461,14 @@ NodeStageKernel(const __grid_constant__ StageArgs p, const __grid_constant__ Lin
     const NodeThread g(p, tid, p.block_begin + t, 0, smem);
     NodeGather(p, tab, g);
     asm volatile("cp.async.commit_group;" ::: "memory");
+    if (kAffine && g.n == S::kProducerWarp) { NodeAffineRows(g); MbarArrive(bytes + S::kOffBar + 16); }
   }
   for (int it = 0; t < n_tiles; t += gridDim.x, ++it) {
     const int buf = it & 1;
     const bool more = t + (int)gridDim.x < n_tiles;
     const NodeThread g(p, tid, p.block_begin + t, buf, smem);
     MbarWait(bytes + S::kOffBar + 8 * buf, (it >> 1) & 1);
+    if (kAffine) MbarWait(bytes + S::kOffBar + 16 + 8 * buf, (it >> 1) & 1);
     if (p.mode >= kModeRk3b && g.active) {   // the second stream of the update: bring it towards the SM early
       const double *u0 = p.u0 + ((size_t)g.tile * S::F + g.n * 5) * kTile + g.lane;
 #pragma unroll
@@ -437,6 +481,12 @@ NodeStageKernel(const __grid_constant__ StageArgs p, const __grid_constant__ Lin
     NodePhaseB(tab, g, &r);
     __syncthreads();                       // F^ may be overwritten by the next tile
     NodeStash(g, r);
+    if (kAffine && more && g.n == S::kProducerWarp) {   // this warp has no face point: the next tile's metric meanwhile.  Its
+      // buffer was last read in the tile before this one, which every warp left before this tile's first barrier.
+      MbarWait(bytes + S::kOffBar + 8 * (buf ^ 1), ((it + 1) >> 1) & 1);
+      NodeAffineRows(NodeThread(p, tid, p.block_begin + t + gridDim.x, buf ^ 1, smem));
+      MbarArrive(bytes + S::kOffBar + 16 + 8 * (buf ^ 1));
+    }
     asm volatile("cp.async.wait_group 0;" ::: "memory");   // my gathers for this tile
     NodePhaseC<kRiemann, kAffine>(p, tab, g, smem, &r);
     if (more) {                            // my slots of sN are free: the next tile's neighbours
@@ -462,6 +512,7 @@ void RunNodeStageTileOnHost(const StageArgs &p, const LineTables &tab, int tile,
     bytes[S::kOffCode + x] = p.code[(size_t)tile * 6 * kTile + x];
   }
   static NodeRegs regs[S::kThreads];
+  if (kAffine) for (int lane = 0; lane < kTile; ++lane) NodeAffineRows(NodeThread(p, S::kProducerWarp * 32 + lane, tile, 0, smem));
   for (int t = 0; t < S::kThreads; ++t) {
     const NodeThread g(p, t, tile, 0, smem);
     NodeGather(p, tab, g);

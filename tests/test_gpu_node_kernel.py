@@ -40,6 +40,26 @@ def test_golden_residual_and_rk3(name, degree, scheme, riemann):
 
 
 @pytest.mark.parametrize("riemann", [capi.EXACT, capi.HLLC, capi.AUSM])
+def test_affine_mesh_takes_the_per_tile_metric(riemann):
+    """A sheared box (every cell the same parallelepiped, no face aligned with an axis): the affine instantiation, all
+    boundary kinds of the golden cases, against the oracle."""
+    m = meshmod.box(9, 8, 7, hi=(1.0, 0.8, 0.7))
+    shear = np.array([[1.0, 0.3, 0.1], [0.0, 1.0, 0.2], [0.0, 0.0, 1.0]])
+    m = meshmod.HexMesh(nodes=m.nodes @ shear.T, cells=m.cells, bfaces=m.bfaces, btags=m.btags)
+    u = cases.noisy_state(cell_points(m.nodes, m.cells, 2), seed=3)
+    o = oc.Oracle(m, 2, 0, riemann)
+    cases.apply_bcs_oracle(o)
+    sp = Spatial(Part(m), degree=2, riemann=riemann, device=0)
+    cases.apply_bcs_spatial(sp, cases.MIXED_BCS)
+    sp.SetSolutionColumn(u)
+    sp.SetTime(0.3)
+    assert relerr(sp.GetResidualColumn(), o.residual(u, 0.3)) < 1e-12
+    sp.SetSolutionColumn(u)
+    RungeKutta(3).Update(sp, 0.1, 1e-3)
+    assert relerr(sp.GetSolutionColumn(), o.rk_update(u, 3, 0.1, 1e-3)) < 1e-12
+
+
+@pytest.mark.parametrize("riemann", [capi.EXACT, capi.HLLC, capi.AUSM])
 def test_many_tiles_per_cta_all_rk_orders(riemann):
     """6 000 cells = 188 tiles on 148 CTAs: every CTA's pipeline (prefetch of the next tile, both buffers, the last,
     partly filled tile) is exercised; walls all around."""
@@ -57,12 +77,13 @@ def test_many_tiles_per_cta_all_rk_orders(riemann):
         assert relerr(sp.GetSolutionColumn(), o.rk_update(u, order, 0.0, 1e-3)) < 1e-12
 
 
-@pytest.mark.parametrize("world", [2, 3])
-def test_peer_step_on_several_parts(world):
+@pytest.mark.parametrize("world,warp", [(2, 0.1), (3, 0.1), (3, 0.0)])
+def test_peer_step_on_several_parts(world, warp):
     """mcfd_peer_step_group with the node kernel: ghost states read from the receive stage, the producer thread polls
-    for the neighbours' delivery, send cells packed by the kernel."""
+    for the neighbours' delivery, send cells packed by the kernel.  warp = 0: a mesh of parallelepipeds, i.e. the
+    instantiation with the per-tile metric (what the library picks for such a mesh by itself)."""
     import torch
-    m = meshmod.scramble(meshmod.box(12, 8, 6, warp=0.1, seed=2), seed=3)
+    m = meshmod.scramble(meshmod.box(12, 8, 6, hi=(1.2, 0.8, 0.6), warp=warp, seed=2), seed=3)
     parts = (np.arange(m.n_cells) * world // m.n_cells).astype(np.int32)
     u = cases.noisy_state(cell_points(m.nodes, m.cells, 2), seed=9)
     o = oc.Oracle(m, 2, 0, capi.HLLC)
