@@ -556,7 +556,7 @@ int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
   ctx->use_lines = !viscous && ctx->q == 3 && (config->scheme == MCFD_FR_LOBATTO || config->scheme == MCFD_DG_LOBATTO);
   if (ctx->use_lines) {
     // "lines" | "nodes" for A/B runs; without it mcfd_set_mesh decides: the node kernel where every cell is a
-    // parallelepiped (146 against 155 us per stage on the benchmark box), the node-line kernel elsewhere (164 : 166)
+    // parallelepiped (141 against 155 us per stage on the benchmark box), the node-line kernel elsewhere (164 : 166)
     const char *which = std::getenv("MCFD_STAGE_KERNEL");
     ctx->stage_kernel_forced = which != nullptr;
     ctx->use_nodes = which ? std::string(which) == "nodes" : false;
