@@ -423,6 +423,11 @@ int mcfd_eigen_matrices(mcfd_ctx *ctx, int64_t n, const double *conservative, co
                         double *right);
 
 int64_t mcfd_launch_count(const mcfd_ctx *ctx);
+/* Which kernel a stage of this context launches, as a static string: "NodeStageKernel<affine>" (inviscid lumped Lobatto
+ * schemes at p = 2 on a mesh whose local cells are all parallelepipeds up to rounding), "NodeStageKernel<general>" /
+ * "LineStageKernel<affine|general>" (the same schemes otherwise, or as MCFD_STAGE_KERNEL=nodes|lines says),
+ * "StageKernel", "DgmStageKernel".  Decided by mcfd_set_mesh; "?" before it.  No counterpart in the reference. */
+const char *mcfd_stage_kernel(const mcfd_ctx *ctx);
 /* Duration in ms of the stage kernels launched since the last call with reset != 0, measured with
  * CUDA events on the context's stream when timing is enabled (bench.py's roofline leg). */
 int mcfd_enable_kernel_timing(mcfd_ctx *ctx, int enable);

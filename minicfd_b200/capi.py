@@ -97,6 +97,7 @@ SYMBOLS = {
     "mcfd_limiter_weno_eigen": (C.c_int, [_P, C.c_double, C.c_double, C.c_int]),
     "mcfd_eigen_matrices": (C.c_int, [_P, C.c_int64, _D, _D, _D, _D]),
     "mcfd_launch_count": (C.c_int64, [_P]),
+    "mcfd_stage_kernel": (C.c_char_p, [_P]),
     "mcfd_enable_kernel_timing": (C.c_int, [_P, C.c_int]),
     "mcfd_kernel_time": (C.c_int, [_P, _D, _I64, C.c_int]),
     "mcfd_riemann_flux": (C.c_int, [_P, C.c_int32, C.c_int64, _D, _D, _D, _D]),
@@ -464,6 +465,10 @@ class Context:
 
     def launch_count(self):
         return int(self.lib.mcfd_launch_count(self.h))
+
+    def stage_kernel(self):
+        """Which kernel a stage of this context launches (mcfd_stage_kernel)."""
+        return self.lib.mcfd_stage_kernel(self.h).decode()
 
     def enable_kernel_timing(self, on=True):
         self._check(self.lib.mcfd_enable_kernel_timing(self.h, int(on)))

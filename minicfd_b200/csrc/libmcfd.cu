@@ -2049,6 +2049,13 @@ int mcfd_shuffle_connectivity(int32_t device, int64_t n_cells, int32_t npe, int6
 }
 
 int64_t mcfd_launch_count(const mcfd_ctx *ctx) { return ctx ? ctx->launches : 0; }
+const char *mcfd_stage_kernel(const mcfd_ctx *ctx) {
+  if (!ctx || !ctx->has_mesh) return "?";
+  if (ctx->cfg.scheme == MCFD_DG_GENERAL) return "DgmStageKernel";
+  if (!ctx->use_lines) return "StageKernel";
+  if (ctx->use_nodes) return ctx->mesh.all_affine ? "NodeStageKernel<affine>" : "NodeStageKernel<general>";
+  return ctx->mesh.all_affine ? "LineStageKernel<affine>" : "LineStageKernel<general>";
+}
 
 int mcfd_enable_kernel_timing(mcfd_ctx *ctx, int enable) {
   if (!ctx) return MCFD_ERR_ARG;

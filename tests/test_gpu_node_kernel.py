@@ -110,3 +110,17 @@ def test_peer_step_on_several_parts(world, warp):
     for sp, p in zip(S, P):
         p.scatter_to_global(sp.GetSolutionColumn(), 135, got)
     assert relerr(got, ref) < 1e-12
+
+
+def test_library_picks_the_kernel_by_the_mesh(monkeypatch):
+    """Without MCFD_STAGE_KERNEL: a box whose vertex coordinates are not exact in binary (i * 10 / 7: the bilinear
+    coefficients come out as 1e-16, not 0) is still a mesh of parallelepipeds and takes the node kernel with the
+    per-tile metric; a warped mesh takes the node-line kernel; p = 3 and viscous contexts their own."""
+    monkeypatch.delenv("MCFD_STAGE_KERNEL")
+    box = meshmod.box(7, 5, 3, hi=(10.0, 10.0, 10.0))
+    assert Spatial(Part(box), degree=2, riemann=capi.HLLC, device=0).ctx.stage_kernel() == "NodeStageKernel<affine>"
+    warped = meshmod.box(7, 5, 3, hi=(10.0, 10.0, 10.0), warp=0.1, seed=1)
+    assert Spatial(Part(warped), degree=2, riemann=capi.HLLC, device=0).ctx.stage_kernel() == "LineStageKernel<general>"
+    assert Spatial(Part(box), degree=3, riemann=capi.HLLC, device=0).ctx.stage_kernel() == "StageKernel"
+    monkeypatch.setenv("MCFD_STAGE_KERNEL", "lines")
+    assert Spatial(Part(box), degree=2, riemann=capi.HLLC, device=0).ctx.stage_kernel() == "LineStageKernel<affine>"
