@@ -981,14 +981,21 @@ class EnergyBasedViscosity : public R {
   using Scalar = typename R::Scalar;
   using Viscosity = EnergyBasedViscosity;                   // viscosity.hpp:547
   using Property = algebra::Vector<Scalar, R::kComponents>;  // viscosity.hpp:54
-  static constexpr int kDiffusion = MCFD_CELL_VISCOSITY_DDG;
+  // over a diffusive base (Navier-Stokes, demo/laminar/shocked.hpp:100-111) the base's flux stays and the artificial
+  // one comes on top (viscosity.hpp:76-139); over Direct<Isotropic> the rule owns the viscosities alone
+  static constexpr bool kDiffusiveBase = R::kDiffusion == MCFD_NAVIER_STOKES_DDG;
+  static constexpr int kDiffusion = kDiffusiveBase ? MCFD_NAVIER_STOKES_CELL_VISCOSITY_DDG : MCFD_CELL_VISCOSITY_DDG;
 
   template <class Spatial>
   static void Initialize(Spatial *spatial_ptr) {   // viscosity.hpp:549-554
     ctx_ = spatial_ptr->context();
     n_cells_ = spatial_ptr->part().CountLocalCells() + spatial_ptr->part().CountGhostCells();
     using D = typename R::Diffusion;
-    b200::Check(mcfd_set_diffusion(ctx_, D::beta_0_, D::beta_1_, 0.0, 1.0), ctx_, "mcfd_set_diffusion");
+    if constexpr (kDiffusiveBase) {
+      b200::Check(mcfd_set_diffusion(ctx_, D::beta_0_, D::beta_1_, D::GetProperty().nu, D::GetProperty().prandtl), ctx_, "mcfd_set_diffusion");
+    } else {
+      b200::Check(mcfd_set_diffusion(ctx_, D::beta_0_, D::beta_1_, 0.0, 1.0), ctx_, "mcfd_set_diffusion");
+    }
     b200::Check(mcfd_build_damping_matrices(ctx_), ctx_, "mcfd_build_damping_matrices");
     SetTimeScale(1.0);
   }

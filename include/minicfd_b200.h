@@ -75,7 +75,12 @@ typedef enum {
  * (include/mini/riemann/diffusive/linear.hpp:103-121; demo/euler/sourceless.hpp:88-93 composes it for the VISCOSITY
  * build), generalised to one viscosity per component and cell, which is the flux EnergyBasedViscosity adds
  * (include/mini/spatial/viscosity.hpp:68-71, 114-129): F_k -= nu_k grad u_k. */
-typedef enum { MCFD_INVISCID = 0, MCFD_NAVIER_STOKES_DDG = 1, MCFD_CELL_VISCOSITY_DDG = 2 } mcfd_diffusion;
+/* MCFD_NAVIER_STOKES_CELL_VISCOSITY_DDG = both: EnergyBasedViscosity over a diffusive base (demo/laminar/shocked.hpp:
+ * 100-111; viscosity.hpp:76-129): the base's Navier-Stokes flux with the properties of mcfd_set_diffusion, then
+ * F_k -= nu_k grad u_k with the per-cell viscosities (zero until set or updated); on no-slip walls the base's wall flux,
+ * then the base's and the artificial normal fluxes of the cell's own gradient (viscosity.hpp:132-139). */
+typedef enum { MCFD_INVISCID = 0, MCFD_NAVIER_STOKES_DDG = 1, MCFD_CELL_VISCOSITY_DDG = 2,
+               MCFD_NAVIER_STOKES_CELL_VISCOSITY_DDG = 3 } mcfd_diffusion;
 
 typedef struct {
   int32_t scheme;    /* mcfd_scheme */

@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(HERE, "libminicfd_b200.so")
 
 FR_LOBATTO, DG_LOBATTO, FR_GENERAL, DG_GENERAL = 0, 1, 2, 3
 EXACT, HLLC, AUSM = 0, 1, 2
-INVISCID, NAVIER_STOKES_DDG, CELL_VISCOSITY_DDG = 0, 1, 2
+INVISCID, NAVIER_STOKES_DDG, CELL_VISCOSITY_DDG, NAVIER_STOKES_CELL_VISCOSITY_DDG = 0, 1, 2, 3
 (BC_INVISCID_WALL, BC_SUPERSONIC_OUTLET, BC_SUPERSONIC_INLET, BC_SUBSONIC_INLET, BC_SUBSONIC_OUTLET,
  BC_SMART, BC_NO_SLIP_WALL) = range(7)
 

@@ -149,7 +149,8 @@ enum : int {
   kDiffIsotropic = 2,      // diffusive::Direct<diffusive::Isotropic<Scalar, 5>> / EnergyBasedViscosity: nu per component and cell
   // EnergyBasedViscosity::BuildDampingMatrices (spatial/viscosity.hpp:299-384): the viscous operator alone, nu = 1,
   // every neighbour and every boundary side zero (AddFluxToHolder / AddFluxToSharer, fr/general.hpp:356-408)
-  kDiffProbe = 3
+  kDiffProbe = 3,
+  kDiffNsIsotropic = 4     // EnergyBasedViscosity over the Navier-Stokes base: both of the above (viscosity.hpp:76-129)
 };
 
 enum : int {
@@ -568,8 +569,10 @@ MCFD_HD void StagePhaseA(const StageArgs &p, int tid, int bid, double *smem,
 #pragma unroll
         for (int c = 0; c < 5; ++c) gr[x][c] = src[(x * 5 + c) * kTile];
       }
-      if (kViscous == kDiffNavierStokes) {
+      if (kViscous == kDiffNavierStokes || kViscous == kDiffNsIsotropic) {
         NsMinusFluxMatrix(p.vis, u, gr, fx);
+      }
+      if (kViscous == kDiffNavierStokes) {
       } else if (kViscous == kDiffProbe) {
         const double one[5] = {1, 1, 1, 1, 1};
 #pragma unroll
@@ -778,9 +781,10 @@ MCFD_HD void StagePhaseB2(const StageArgs &p, int tid, int bid, double *smem) {
               gc[x][c] = (go[r] + gn[r]) * 0.5 + (pen0 * o[x]) * (cur.v[c] - cur.u[c]) - pen1 * (ho[r] + hb[r]);
             }
           }
-          if (kViscous == kDiffNavierStokes) {
+          if (kViscous == kDiffNavierStokes || kViscous == kDiffNsIsotropic) {
             NsMinusFluxNormal(p.vis, uc, gc, hs * nx, hs * ny, hs * nz, fl);
-          } else {   // property = (mine + neighbour's) / 2, fr/general.hpp:331-335
+          }
+          if (kViscous != kDiffNavierStokes) {   // property = (mine + neighbour's) / 2, fr/general.hpp:331-335
             double nu[5];
 #pragma unroll
             for (int c = 0; c < 5; ++c)
@@ -809,9 +813,14 @@ MCFD_HD void StagePhaseB2(const StageArgs &p, int tid, int bid, double *smem) {
 #pragma unroll
             for (int c = 0; c < 5; ++c) gr[x][c] = go[(x * 5 + c) * kTile];
           }
-          if (kViscous == kDiffNavierStokes) {
+          if (kViscous == kDiffNavierStokes || kViscous == kDiffNsIsotropic) {
             NsMinusFluxNoSlip(p.vis, wall, cur.u, gr, inv * nx, inv * ny, inv * nz, p.vis.beta0 * Rcp(dh), fl);
-          } else {   // linear.hpp:85-91: the cell's own gradient, no penalty
+          }
+          // over a diffusive base EnergyBasedViscosity::MinusViscousFluxOnNoSlipWall goes on with its own
+          // MinusViscousFlux(flux, nu, value, gradient, normal), which subtracts the BASE's normal flux of the
+          // unpenalised gradient once more before the artificial one (viscosity.hpp:114-139)
+          if (kViscous == kDiffNsIsotropic) NsMinusFluxNormal(p.vis, cur.u, gr, inv * nx, inv * ny, inv * nz, fl);
+          if (kViscous != kDiffNavierStokes) {   // linear.hpp:85-91: the cell's own gradient, no penalty
             double nu[5];
 #pragma unroll
             for (int c = 0; c < 5; ++c) nu[c] = p.cell_nu[((size_t)g.tile * 5 + c) * kTile + g.tl];
@@ -831,7 +840,7 @@ MCFD_HD void StagePhaseB2(const StageArgs &p, int tid, int bid, double *smem) {
             fm[1 + x][x] += pr.p;
             fm[4][x] = h0 * vel[x];
           }
-          if (kViscous == kDiffNavierStokes || kViscous == kDiffIsotropic) {   // the cached flux carried the viscous part too
+          if (kViscous == kDiffNavierStokes || kViscous == kDiffIsotropic || kViscous == kDiffNsIsotropic) {   // the cached flux carried the viscous part too
             const double *go = p.grad + ((size_t)g.tile * G::N * 15 + n * 15) * kTile + g.tl;
             double gr[3][5], fx[3][5];
 #pragma unroll
@@ -839,9 +848,10 @@ MCFD_HD void StagePhaseB2(const StageArgs &p, int tid, int bid, double *smem) {
 #pragma unroll
               for (int c = 0; c < 5; ++c) { gr[x][c] = go[(x * 5 + c) * kTile]; fx[x][c] = fm[c][x]; }
             }
-            if (kViscous == kDiffNavierStokes) {
+            if (kViscous == kDiffNavierStokes || kViscous == kDiffNsIsotropic) {
               NsMinusFluxMatrix(p.vis, cur.u, gr, fx);
-            } else {
+            }
+            if (kViscous != kDiffNavierStokes) {
               double nu[5];
 #pragma unroll
               for (int c = 0; c < 5; ++c) nu[c] = p.cell_nu[((size_t)g.tile * 5 + c) * kTile + g.tl];

@@ -287,6 +287,7 @@ cudaError_t LaunchStageViscous(mcfd_ctx *ctx, StageArgs const &a, int n_blocks) 
   }
   if (ctx->cfg.scheme == MCFD_FR_GENERAL)   // fr::General on the Navier-Stokes Riemann type
     return LaunchStageDiffusive<Q, CPB, NW, kDiffNavierStokes, true>(ctx, a, n_blocks);
+  if (ctx->cfg.diffusion == MCFD_NAVIER_STOKES_CELL_VISCOSITY_DDG) return LaunchStageDiffusive<Q, CPB, NW, kDiffNsIsotropic>(ctx, a, n_blocks);
   return ctx->cfg.diffusion == MCFD_NAVIER_STOKES_DDG ? LaunchStageDiffusive<Q, CPB, NW, kDiffNavierStokes>(ctx, a, n_blocks)
                                                       : LaunchStageDiffusive<Q, CPB, NW, kDiffIsotropic>(ctx, a, n_blocks);
 }
@@ -354,6 +355,11 @@ cudaError_t LaunchDgmQ(mcfd_ctx *ctx, DgmArgs const &a, int t0, int n_tiles) {
   default: DgmStageKernel<Q, kAusm><<<n_tiles, kTile, 0, ctx->stream>>>(a, t0); break;
   }
   return cudaGetLastError();
+}
+
+// contexts with one viscosity per cell and component: alone, or on top of the Navier-Stokes terms
+static bool HasCellViscosity(const mcfd_ctx *ctx) {
+  return ctx->cfg.diffusion == MCFD_CELL_VISCOSITY_DDG || ctx->cfg.diffusion == MCFD_NAVIER_STOKES_CELL_VISCOSITY_DDG;
 }
 
 // Launch the stage kernel over CTA blocks [block_begin, block_end).
@@ -519,7 +525,7 @@ int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
     return Fail(nullptr, MCFD_ERR_ARG, "the reference's DG schemes have no diffusive terms");
   if (config->riemann < MCFD_EXACT || config->riemann > MCFD_AUSM)
     return Fail(nullptr, MCFD_ERR_ARG, "unknown Riemann solver");
-  if (config->diffusion < MCFD_INVISCID || config->diffusion > MCFD_CELL_VISCOSITY_DDG)
+  if (config->diffusion < MCFD_INVISCID || config->diffusion > MCFD_NAVIER_STOKES_CELL_VISCOSITY_DDG)
     return Fail(nullptr, MCFD_ERR_ARG, "unknown diffusion model");
   // the reference's DG schemes carry no diffusive terms at all (spatial/dg/*.hpp); fr::General has them for any Riemann
   // type, built here for Navier-Stokes
@@ -527,10 +533,11 @@ int mcfd_create(const mcfd_config *config, mcfd_ctx **ctx_out) {
     return Fail(nullptr, MCFD_ERR_ARG, "the reference's DG schemes have no diffusive terms; use MCFD_FR_LOBATTO or MCFD_FR_GENERAL");
   if (config->k_local != 0 && config->k_local != 1) return Fail(nullptr, MCFD_ERR_ARG, "k_local must be 0 or 1");
   if (config->k_local && (config->scheme == MCFD_DG_LOBATTO || config->scheme == MCFD_DG_GENERAL ||
-                          config->diffusion == MCFD_CELL_VISCOSITY_DDG))
+                          config->diffusion == MCFD_CELL_VISCOSITY_DDG || config->diffusion == MCFD_NAVIER_STOKES_CELL_VISCOSITY_DDG))
     return Fail(nullptr, MCFD_ERR_ARG, "k_local is built for the FR schemes on Euler and Navier-Stokes");
-  if (config->diffusion == MCFD_CELL_VISCOSITY_DDG && config->scheme != MCFD_FR_LOBATTO)
-    return Fail(nullptr, MCFD_ERR_ARG, "MCFD_CELL_VISCOSITY_DDG is built for MCFD_FR_LOBATTO only");
+  if ((config->diffusion == MCFD_CELL_VISCOSITY_DDG || config->diffusion == MCFD_NAVIER_STOKES_CELL_VISCOSITY_DDG) &&
+      config->scheme != MCFD_FR_LOBATTO)
+    return Fail(nullptr, MCFD_ERR_ARG, "the per-cell viscosity is built for MCFD_FR_LOBATTO only");
   int n_dev = 0;
   cudaError_t e = cudaGetDeviceCount(&n_dev);
   if (e != cudaSuccess || n_dev == 0)
@@ -652,8 +659,8 @@ int mcfd_set_mesh(mcfd_ctx *ctx, int64_t n_nodes, const double *xyz, int64_t n_l
     MCFD_CUDA(ctx, ctx->hn.Alloc((size_t)ctx->n_tiles * 6 * ctx->q * ctx->q * 15 * kTile));
     MCFD_CUDA(ctx, cudaMemset(ctx->grad.p, 0, ctx->grad.n * sizeof(double)));
     MCFD_CUDA(ctx, cudaMemset(ctx->hn.p, 0, ctx->hn.n * sizeof(double)));
-    if (ctx->cfg.diffusion == MCFD_CELL_VISCOSITY_DDG) {   // starts uniform at the nu of mcfd_set_diffusion
-      std::vector<double> nu((size_t)ctx->n_tiles * 5 * kTile, ctx->vis.nu);
+    if (HasCellViscosity(ctx)) {   // starts uniform at the nu of mcfd_set_diffusion; at zero on top of Navier-Stokes
+      std::vector<double> nu((size_t)ctx->n_tiles * 5 * kTile, ctx->cfg.diffusion == MCFD_CELL_VISCOSITY_DDG ? ctx->vis.nu : 0.0);
       MCFD_CUDA(ctx, ctx->cell_nu.Alloc(nu.size()));
       MCFD_CUDA(ctx, cudaMemcpy(ctx->cell_nu.p, nu.data(), nu.size() * sizeof(double), cudaMemcpyHostToDevice));
     }
@@ -841,8 +848,8 @@ int mcfd_set_diffusion(mcfd_ctx *ctx, double beta_0, double beta_1, double nu, d
 
 int mcfd_build_damping_matrices(mcfd_ctx *ctx) {
   if (int s = RequireMesh(ctx)) return s;
-  if (ctx->cfg.diffusion != MCFD_CELL_VISCOSITY_DDG)
-    return Fail(ctx, MCFD_ERR_STATE, "the context was not created with MCFD_CELL_VISCOSITY_DDG");
+  if (!HasCellViscosity(ctx))
+    return Fail(ctx, MCFD_ERR_STATE, "the context was not created with a per-cell viscosity (MCFD_CELL_VISCOSITY_DDG, MCFD_NAVIER_STOKES_CELL_VISCOSITY_DDG)");
   if (ctx->rk_order) return Fail(ctx, MCFD_ERR_STATE, "an RK step is open");
   const int n = ctx->n_nodes;
   const size_t state = (size_t)ctx->n_tiles * ctx->fields * kTile;
@@ -943,8 +950,8 @@ int mcfd_get_cell_viscosity(mcfd_ctx *ctx, double *nu) {
 
 int mcfd_set_cell_viscosity(mcfd_ctx *ctx, int64_t n_cells, const double *nu) {
   if (int s = RequireMesh(ctx)) return s;
-  if (ctx->cfg.diffusion != MCFD_CELL_VISCOSITY_DDG)
-    return Fail(ctx, MCFD_ERR_STATE, "the context was not created with MCFD_CELL_VISCOSITY_DDG");
+  if (!HasCellViscosity(ctx))
+    return Fail(ctx, MCFD_ERR_STATE, "the context was not created with a per-cell viscosity (MCFD_CELL_VISCOSITY_DDG, MCFD_NAVIER_STOKES_CELL_VISCOSITY_DDG)");
   if (!nu || n_cells != ctx->n_cells) return Fail(ctx, MCFD_ERR_ARG, "need [n_local + n_ghost][5] values");
   std::vector<double> rows((size_t)n_cells * 5);
   std::copy(nu, nu + n_cells * 5, rows.begin());

@@ -868,6 +868,9 @@ template <class Unrotated>
 using Energy = mini::spatial::EnergyBasedViscosity<Part, IsoViscous<Unrotated>>;
 using EExact = Energy<mini::riemann::euler::Exact<Gas, 3>>;
 using EHllc = Energy<mini::riemann::euler::HartenLaxLeerContact<Gas, 3>>;
+// the same rule over a DIFFUSIVE base, Navier-Stokes + direct DG (demo/laminar/shocked.hpp:100-111): only to look at
+// what the reference's own set-up makes of it (tests/test_oracle_pinned.py::test_energy_viscosity_over_navier_stokes_base)
+using ENsHllc = mini::spatial::EnergyBasedViscosity<Part, VHllc>;
 
 // the kLocal == true expansion (coefficients = det(J) u), as the reference's laminar drivers use it for FR
 // (demo/laminar/shockless.hpp:62-69)
@@ -955,6 +958,9 @@ static SolverBase *Create(int scheme, int riemann, GlobalMesh &&mesh) {
     case 0: return new SolverImpl<sp::WithViscosity<sp::fr::Lobatto<Part, EExact>>>(std::move(mesh));
     case 1: return new SolverImpl<sp::WithViscosity<sp::fr::Lobatto<Part, EHllc>>>(std::move(mesh));
     }
+  } else if (scheme == 20) {   // single part only, HLLC only
+    if (mesh.n_parts != 1 || riemann != 1) return nullptr;
+    return new SolverImpl<sp::WithViscosity<sp::fr::Lobatto<Part, ENsHllc>>>(std::move(mesh));
   } else if (scheme == 6) {
     switch (riemann) {
     case 0: return new SolverImpl<sp::fr::Lobatto<Part, IExact>>(std::move(mesh));

@@ -152,6 +152,7 @@ def cell_viscosities(n_cells, seed=1):
 
 # ---- EnergyBasedViscosity + WithViscosity ----------------------------------------------------------
 ENERGY_GOLDEN_CASES = [("energy_p2_hllc", 2, 1), ("energy_p3_hllc", 3, 1)]
+ENERGY_NS_GOLDEN_CASES = [("energy_ns_p2_hllc", 2, 1)]   # EnergyBasedViscosity over the Navier-Stokes base
 ENERGY_BETAS = (2.0, 1.0 / 12)
 ENERGY_AMP = 5e-2          # noise level at which some, not all, (cell, component) pairs get a viscosity
 

@@ -19,8 +19,12 @@ import refapi  # noqa: E402
 from minicfd_b200.part import cell_points  # noqa: E402
 
 
-def main():
+def main(only=None):
     m = cases.small_mesh()
+    if only == "energy_ns":      # `python tests/golden/make_golden.py energy_ns`: just the files added last
+        for k in ("GOLDEN_CASES", "VISCOUS_GOLDEN_CASES", "ISO_GOLDEN_CASES", "ENERGY_GOLDEN_CASES", "DGM_GOLDEN_CASES",
+                  "DGM_WENO_GOLDEN_CASES", "LOCAL_GOLDEN_CASES", "WENO_GOLDEN_CASES", "WENO_EIGEN_GOLDEN_CASES"):
+            setattr(cases, k, [])
     for name, degree, scheme, riemann in cases.GOLDEN_CASES:
         r = refapi.Ref(m, degree=degree, scheme=scheme, riemann=riemann)
         cases.apply_bcs_ref(r)
@@ -62,6 +66,21 @@ def main():
         r = refapi.Ref(m, degree=degree, scheme=refapi.FR_ENERGY_VISCOSITY, riemann=riemann,
                        viscous=cases.ENERGY_BETAS + (0.0, 0.708))
         cases.apply_bcs_ref(r)
+        u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), amp=cases.ENERGY_AMP)
+        damping = r.damping_matrices()          # zeroes the solution
+        r.set_solution(u)                       # SetSolutionColumn -> UpdateProperties
+        nu = r.cell_viscosity()
+        dt = r.time_step(1.0, 3)
+        res = r.residual(cases.GOLDEN_T)
+        r.rk_update(3, 0.0, cases.GOLDEN_DT, 1)
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), u=u, damping=damping[:4], nu=nu, dt=dt, residual=res,
+                            u_rk3=r.get_solution(), nu_rk3=r.cell_viscosity(),
+                            nodes=m.nodes, cells=m.cells, bfaces=m.bfaces, btags=m.btags)
+        print(name, int((nu > 0).sum()), "of", nu.size, "viscosities non-zero; dt", dt)
+    # the same rule over the Navier-Stokes base (demo/laminar/shocked.hpp:100-111), viscous boundary set-up, p = 2
+    for name, degree, riemann in cases.ENERGY_NS_GOLDEN_CASES:
+        r = refapi.Ref(m, degree=degree, scheme=refapi.FR_ENERGY_VISCOSITY_NS, riemann=riemann, viscous=cases.VISCOUS)
+        cases.apply_viscous_ref(r)
         u = cases.noisy_state(cell_points(m.nodes, m.cells, degree), amp=cases.ENERGY_AMP)
         damping = r.damping_matrices()          # zeroes the solution
         r.set_solution(u)                       # SetSolutionColumn -> UpdateProperties
@@ -146,4 +165,4 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    main(sys.argv[1] if len(sys.argv) > 1 else None)

@@ -21,7 +21,8 @@ void RunStage(StageArgs a, int n_blocks) {
   using G = StageGeometry<Q, CPB, NW>;
   std::vector<double> smem(G::kSharedBytes / sizeof(double) + 1);
   for (int b = 0; b < n_blocks; ++b) {
-    if (a.grad && a.cell_nu) RunStageBlockOnHost<Q, R, CPB, NW, false, kDiffIsotropic>(a, b, smem.data());
+    if (a.grad && a.cell_nu && a.vis.nu != 0) RunStageBlockOnHost<Q, R, CPB, NW, false, kDiffNsIsotropic>(a, b, smem.data());   // over a Navier-Stokes base
+    else if (a.grad && a.cell_nu) RunStageBlockOnHost<Q, R, CPB, NW, false, kDiffIsotropic>(a, b, smem.data());
     else if (a.grad && c_tab.general) RunStageBlockOnHost<Q, R, CPB, NW, true, kDiffNavierStokes>(a, b, smem.data());
     else if (a.grad) RunStageBlockOnHost<Q, R, CPB, NW, false, kDiffNavierStokes>(a, b, smem.data());
     else if (c_tab.general) RunStageBlockOnHost<Q, R, CPB, NW, true>(a, b, smem.data());

@@ -13,6 +13,7 @@ _libs: dict[int, C.CDLL] = {}
 CB = C.CFUNCTYPE(None, C.c_int, C.POINTER(C.c_double), C.c_double, C.POINTER(C.c_double), C.c_void_p)
 
 FR, DG, FR_GENERAL, FR_VISCOUS, FR_WENO_LAZY, FR_WENO_EIGEN, FR_ISOTROPIC, FR_ENERGY_VISCOSITY, FR_GENERAL_VISCOUS, DG_GENERAL, DG_GENERAL_WENO_LAZY, FR_LOCAL, FR_LOCAL_VISCOUS, DG_WENO_LAZY = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13
+FR_ENERGY_VISCOSITY_NS = 20   # EnergyBasedViscosity over the Navier-Stokes base (demo/laminar/shocked.hpp:100-111); HLLC, one part
 EXACT, HLLC, AUSM = 0, 1, 2
 # boundary kinds, order of fem.hpp:196-222 as used by ref_harness.cpp
 WALL, SUPERSONIC_OUTLET, SUPERSONIC_INLET, SUBSONIC_INLET, SUBSONIC_OUTLET, SMART, NO_SLIP = range(7)

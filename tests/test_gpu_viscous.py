@@ -329,3 +329,26 @@ def test_energy_based_viscosity_two_parts_with_halo_buffers():
     for sp, p in zip(S, P):
         assert relerr(sp.GetSolutionColumn().reshape(-1, 135), u3.reshape(-1, 135)[p.local_global]) < 1e-12
         assert relerr(sp.ctx.cell_viscosity(), nu3[p.local_global]) < 1e-9
+
+
+@pytest.mark.parametrize("name,degree,riemann", cases.ENERGY_NS_GOLDEN_CASES)
+def test_energy_based_viscosity_over_navier_stokes_golden(name, degree, riemann):
+    """WithViscosity<fr::Lobatto<Part, EnergyBasedViscosity<Part, ConvectionDiffusion<Euler, Direct<NavierStokes>>>>>
+    (demo/laminar/shocked.hpp:100-111): MCFD_NAVIER_STOKES_CELL_VISCOSITY_DDG, against the reference's vectors —
+    damping matrices, viscosities, time step, residual, one RK3 step with the update after every stage."""
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    m = meshmod.HexMesh(nodes=g["nodes"], cells=g["cells"], bfaces=g["bfaces"], btags=g["btags"])
+    sp = Spatial(Part(m), degree=degree, riemann=riemann, device=0, diffusion=capi.NAVIER_STOKES_CELL_VISCOSITY_DDG)
+    cases.apply_viscous_spatial(sp)                            # SetDiffusion(beta_0, beta_1, nu, Pr) + viscous boundaries
+    sp.EnableEnergyBasedViscosity()
+    assert relerr(sp.ctx.damping_matrices()[:4], g["damping"]) < TOL
+    sp.SetSolutionColumn(g["u"])                               # -> UpdateProperties
+    nu = sp.ctx.cell_viscosity()
+    assert np.array_equal(nu > 0, g["nu"] > 0)
+    assert relerr(nu, g["nu"]) < TOL
+    assert sp.GetTimeStep(1.0, 3) == pytest.approx(float(g["dt"]), rel=1e-13)
+    sp.SetTime(cases.GOLDEN_T)
+    assert relerr(sp.GetResidualColumn(), g["residual"]) < TOL
+    RungeKutta(3).Update(sp, 0.0, cases.GOLDEN_DT)
+    assert relerr(sp.GetSolutionColumn(), g["u_rk3"]) < 1e-12
+    assert relerr(sp.ctx.cell_viscosity(), g["nu_rk3"]) < 1e-9

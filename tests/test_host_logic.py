@@ -384,3 +384,33 @@ def test_node_kernel_source_on_host_matches_golden(name, degree, scheme, riemann
     u2 = emuapi.stage(m, degree, scheme, riemann, u1, bvals=bvals(dt), column_u0=u, mode=2, dt=dt, **kw)
     u3 = emuapi.stage(m, degree, scheme, riemann, u2, bvals=bvals(dt / 2), column_u0=u, mode=3, dt=dt, **kw)
     assert relerr(u3, g["u_rk3"]) < 1e-12
+
+
+@pytest.mark.parametrize("name,degree,riemann", cases.ENERGY_NS_GOLDEN_CASES)
+def test_energy_viscosity_over_navier_stokes_kernel_source_on_host(name, degree, riemann):
+    """EnergyBasedViscosity over a DIFFUSIVE base (demo/laminar/shocked.hpp:100-111; viscosity.hpp:76-139): the stage
+    kernel's kDiffNsIsotropic instantiation with the reference's viscosities against the reference's residual (viscous
+    boundary set-up with no-slip walls), and the rule's set-up, which the base does not enter: the damping matrices
+    take the mass row only, where Navier-Stokes adds nothing."""
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    m = meshmod.HexMesh(nodes=g["nodes"], cells=g["cells"], bfaces=g["bfaces"], btags=g["btags"])
+    holder, hf, tags, pts = emuapi.boundary(m, degree)
+    bv = np.zeros(pts.shape[:2] + (5,))
+    for tag, kind in cases.VISCOUS_BCS.items():
+        sel = tags == tag
+        bv[sel] = cases.viscous_bc_function(kind)(pts[sel], cases.GOLDEN_T)
+    res = emuapi.stage(m, degree, 0, riemann, g["u"], tag_kinds=cases.VISCOUS_BCS, bvals=bv, viscous=cases.VISCOUS,
+                       cell_nu=g["nu"])
+    assert relerr(res, g["residual"]) < 1e-12
+    damping, nu, min_dt = emuapi.energy_viscosity(m, degree, cases.VISCOUS[:2], g["u"])
+    assert relerr(damping[:4], g["damping"]) < 1e-12
+    assert np.array_equal(nu > 0, g["nu"] > 0) and relerr(nu, g["nu"]) < 1e-12
+
+
+def test_shocked_type_composition_compiles_against_the_shim():
+    """demo/laminar/shocked.hpp:43-111 spelled against include/mini: EnergyBasedViscosity over ConvectionDiffusion<Euler,
+    Direct<NavierStokes>> compiles and selects the library's Navier-Stokes + per-cell-viscosity path."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    subprocess.check_call(["g++", "-std=c++20", "-fsyntax-only", "-I", os.path.join(root, "include"),
+                           "-I", os.path.join(root, "include", "mini", "b200", "nompi"),
+                           os.path.join(root, "tests", "drivers", "shocked_types.cpp")])
