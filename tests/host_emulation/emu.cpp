@@ -16,12 +16,14 @@ using namespace mcfd;
 
 namespace {
 
+bool g_ns_base = false;   // viscous[4] == 2: the per-cell viscosities come on top of the Navier-Stokes terms
+
 template <int Q, int R, int CPB, int NW>
 void RunStage(StageArgs a, int n_blocks) {
   using G = StageGeometry<Q, CPB, NW>;
   std::vector<double> smem(G::kSharedBytes / sizeof(double) + 1);
   for (int b = 0; b < n_blocks; ++b) {
-    if (a.grad && a.cell_nu && a.vis.nu != 0) RunStageBlockOnHost<Q, R, CPB, NW, false, kDiffNsIsotropic>(a, b, smem.data());   // over a Navier-Stokes base
+    if (a.grad && a.cell_nu && g_ns_base) RunStageBlockOnHost<Q, R, CPB, NW, false, kDiffNsIsotropic>(a, b, smem.data());   // over a Navier-Stokes base
     else if (a.grad && a.cell_nu) RunStageBlockOnHost<Q, R, CPB, NW, false, kDiffIsotropic>(a, b, smem.data());
     else if (a.grad && c_tab.general) RunStageBlockOnHost<Q, R, CPB, NW, true, kDiffNavierStokes>(a, b, smem.data());
     else if (a.grad) RunStageBlockOnHost<Q, R, CPB, NW, false, kDiffNavierStokes>(a, b, smem.data());
@@ -143,7 +145,8 @@ int emu_stage(int degree, int scheme, int riemann, int64_t n_nodes, const double
     grad.assign((size_t)nt * N * 15 * kTile, 0.0);
     hn.assign((size_t)nt * 6 * q * q * 15 * kTile, 0.0);
     h2s = ToTiles(mesh.h2s, 18, nc, nt);
-    const bool klocal = viscous[4] != 0;
+    const bool klocal = viscous[4] == 1;
+    g_ns_base = viscous[4] == 2;
     if (q == 3 && klocal) RunTraceOnHost<3, true>(uin.data(), geom.data(), grad.data(), hn.data(), (int)nc);
     else if (q == 3) RunTraceOnHost<3>(uin.data(), geom.data(), grad.data(), hn.data(), (int)nc);
     else if (klocal) RunTraceOnHost<4, true>(uin.data(), geom.data(), grad.data(), hn.data(), (int)nc);

@@ -399,8 +399,8 @@ def test_energy_viscosity_over_navier_stokes_kernel_source_on_host(name, degree,
     for tag, kind in cases.VISCOUS_BCS.items():
         sel = tags == tag
         bv[sel] = cases.viscous_bc_function(kind)(pts[sel], cases.GOLDEN_T)
-    res = emuapi.stage(m, degree, 0, riemann, g["u"], tag_kinds=cases.VISCOUS_BCS, bvals=bv, viscous=cases.VISCOUS,
-                       cell_nu=g["nu"])
+    res = emuapi.stage(m, degree, 0, riemann, g["u"], tag_kinds=cases.VISCOUS_BCS, bvals=bv,
+                       viscous=list(cases.VISCOUS) + [2.0], cell_nu=g["nu"])    # 2: the viscosities on top of Navier-Stokes
     assert relerr(res, g["residual"]) < 1e-12
     damping, nu, min_dt = emuapi.energy_viscosity(m, degree, cases.VISCOUS[:2], g["u"])
     assert relerr(damping[:4], g["damping"]) < 1e-12
