@@ -69,6 +69,45 @@ def test_partition_and_shuffle_writes_one_file_per_part(tmp_path):
     assert n_local == m.n_cells
 
 
+def test_cpp_reader_builds_the_same_part(tmp_path):
+    """include/mini/b200/partition.hpp: ReadPartitionInfo + BuildPartFromPartition (the C++ side of part.hpp:442-476
+    without its CGNS reads) on the files this module wrote: the shim's Part gets the same local order, ghost cells, halo
+    lists and boundary faces as the Python part.  No GPU involved."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    m, parts, sm = _shuffled(3, seed=11)
+    partition.write_partition_info(str(tmp_path), m, parts, sm)
+    names = {0: "XMin", 1: "XMax", 2: "YMin", 3: "YMax", 4: "ZMin", 5: "ZMax"}
+    with open(tmp_path / "mesh.bin", "wb") as f:
+        i64 = lambda *v: f.write(np.asarray(v, dtype=np.int64).tobytes())
+        i64(len(sm.nodes)); f.write(np.ascontiguousarray(sm.nodes, dtype=np.float64).tobytes())
+        i64(len(sm.cells)); f.write(np.ascontiguousarray(sm.cells, dtype=np.int64).tobytes())
+        f.write(np.ascontiguousarray(sm.cell_metis, dtype=np.int64).tobytes())
+        i64(len(sm.face_sections))
+        for sec in sm.face_sections:
+            name = names[sec["tag"]].encode()
+            i64(len(name)); f.write(name); i64(sec["first"]); i64(len(sec["quads"]))
+            f.write(np.ascontiguousarray(sec["quads"], dtype=np.int64).tobytes())
+    exe = tmp_path / "partition_reader"
+    subprocess.check_call(["g++", "-std=c++20", "-O1", "-I", os.path.join(root, "include"),
+                           os.path.join(root, "tests", "drivers", "partition_reader.cpp"), "-o", str(exe),
+                           "-L", os.path.join(root, "minicfd_b200"), "-lminicfd_b200", "-Wl,-rpath," + os.path.join(root, "minicfd_b200")])
+    tag_order = [sec["tag"] for sec in sm.face_sections]      # the shim numbers its tags in the order of the sections
+    for r in range(3):
+        out = subprocess.run([str(exe), str(tmp_path), str(r), "3", str(tmp_path / "mesh.bin")], capture_output=True, text=True, timeout=60)
+        assert out.returncode == 0, out.stderr
+        rows = {l.split()[0]: [int(x) for x in l.split()[1:]] for l in out.stdout.splitlines() if not l.startswith("local")}
+        p = partition.part_from_partition(partition.read_partition_info(str(tmp_path / "partition" / f"{r}.txt")), sm, r)
+        assert out.stdout.splitlines()[0] == f"local {p.n_local} ghost {p.n_ghost} inner {p.n_inner}"
+        assert rows["ids"] == sm.cell_metis[p.global_ids].tolist()
+        assert rows["neighbours"] == p.neighbours.tolist()
+        assert rows["send_counts"] == [len(x) for x in p.send_cells]
+        assert rows["send"] == np.concatenate(p.send_cells).tolist() and rows["recv"] == np.concatenate(p.recv_cells).tolist()
+        assert rows["bfaces"] == p.bfaces.reshape(-1).tolist()
+        assert [tag_order[t] for t in rows["btags"]] == p.btags.tolist()
+        assert rows["cells"] == p.cell_nodes.reshape(-1).tolist()
+
+
 @pytest.mark.gpu
 def test_parts_from_the_files_advance_like_the_whole_mesh(tmp_path):
     """Three parts built from their partition files, advanced on one GPU with the device-side ghost exchange, against
