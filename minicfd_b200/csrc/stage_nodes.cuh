@@ -62,7 +62,10 @@ __device__ __forceinline__ void MbarWait(void *bar, int parity) {
         "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(addr), "r"(parity) : "memory");
     if (done) return;
-    if (spins > (1ll << 26)) __trap();   // a copy that never lands: fail instead of hanging the device
+    // A copy that never lands: fail instead of hanging the device for ever.  The bound is minutes, not seconds: a tile
+    // with inter cells is armed only after the neighbours' delivery has arrived, and the producer thread may rightly wait
+    // for a late neighbour for up to kPeerSpinLimit polls (about ten seconds) before it gives up and reports it.
+    if (spins > (1ll << 32)) __trap();
   }
 }
 __device__ __forceinline__ void MbarArrive(void *bar) {
