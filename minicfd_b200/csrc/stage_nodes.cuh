@@ -14,9 +14,14 @@
 //     ahead as well, into slots nobody else touches;
 //   * per tile: A (primitive state, metric, the three contravariant fluxes -> shared memory) | barrier |
 //     B (flux divergence from the three node lines through the node) | barrier | C (the node's 0..3 face points:
-//     HLLC, lifted term added in registers) -> D (1 / det J, RK update, store; a send cell's row also packed for the
-//     copy engines).  Nothing is shared after B, so the warps drift apart until the next tile's first barrier and
-//     the uneven number of face points per node (3 at corners, 0 at the centre) is absorbed.
+//     branch-free HLLC; the residual, the state and 1 / det J wait meanwhile in the thread's own 15 rows of the flux
+//     array, which nobody else reads any more, because 72 registers do not hold them beside a Riemann problem) ->
+//     D (1 / det J, RK update, store; a send cell's row also packed for the copy engines).  Nothing is shared after B,
+//     so the warps drift apart until the next tile's first barrier;
+//   * on a mesh of parallelepipeds (kAffine) the warp of the centre node, which has no face point, computes the
+//     cell's metric — columns of J*, their lengths, 1 / det J — once per tile, one tile ahead, into a double-buffered
+//     block guarded by an mbarrier; the other warps read it instead of deriving it per node and per face point.
+// Measured (profiles/r2_kernel_history.md): 141 us per stage on the benchmark box (affine), 166 us on a general mesh.
 // Reference members restated: as in stage_lines.cuh.
 #ifndef MINICFD_B200_STAGE_NODES_CUH_
 #define MINICFD_B200_STAGE_NODES_CUH_
