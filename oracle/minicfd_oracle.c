@@ -470,9 +470,11 @@ static void match_side(const oracle_t *o, int64_t cell, int lf, const double *fx
 }
 
 /* scheme 8 = fr::General (Vincent correction over the whole node line) on the Navier-Stokes Riemann type */
-#define IS_NS(o) ((o)->scheme == 3 || (o)->scheme == 8)
+#define IS_NS(o) ((o)->scheme == 3 || (o)->scheme == 8 || (o)->scheme == 14)
+/* scheme 14: EnergyBasedViscosity over the Navier-Stokes base (viscosity.hpp:76-139): both fluxes, the base's first */
+#define HAS_CELL_NU(o) ((o)->scheme == 6 || (o)->scheme == 14)
 #define IS_GENERAL(o) ((o)->scheme == 2 || (o)->scheme == 8)
-#define IS_LUMPED_FR(o) ((o)->scheme == 0 || (o)->scheme == 3 || (o)->scheme == 6)
+#define IS_LUMPED_FR(o) ((o)->scheme == 0 || (o)->scheme == 3 || (o)->scheme == 6 || (o)->scheme == 14)
 
 static void dgm_setup(struct oracle_s *o, const double *nodes, const int64_t *cn);
 static void dgm_free(struct oracle_s *o);
@@ -906,7 +908,9 @@ static void ns_minus_flux_no_slip(const oracle_t *o, double *f, const double *wa
 /* component-wise isotropic diffusion (diffusive/linear.hpp:66-92 with nu.x = nu.y = nu.z, or
    EnergyBasedViscosity::MinusViscousFlux, spatial/viscosity.hpp:114-129, with one nu per component) */
 static void iso_cell_nu(const oracle_t *o, int64_t c, double *nu) {
-  for (int k = 0; k < 5; ++k) nu[k] = o->cell_nu ? o->cell_nu[c * 5 + k] : o->nu;
+  /* without a table: the uniform value of scheme 6; over the Navier-Stokes base (scheme 14) o->nu is the base's, the
+     artificial viscosities start at zero */
+  for (int k = 0; k < 5; ++k) nu[k] = o->cell_nu ? o->cell_nu[c * 5 + k] : (o->scheme == 14 ? 0.0 : o->nu);
 }
 static void iso_minus_flux_matrix(double F[5][3], const double *nu, const double gc[3][5]) {
   for (int k = 0; k < 5; ++k) for (int x = 0; x < 3; ++x) F[k][x] -= nu[k] * gc[x][k];
@@ -949,13 +953,12 @@ void oracle_residual(void *h, double t, const double *column, double *res) {
     for (int a = 0; a < n; ++a) {
       double F[5][3];
       flux_matrix(&u[(c * n + a) * K], F);
-      if (IS_NS(o) || o->scheme == 6) { /* fem.hpp:397-404 */
+      if (IS_NS(o) || HAS_CELL_NU(o)) { /* fem.hpp:397-404 */
         double gc[3][5], vdummy[5];
         if (o->klocal) local_gradient_hessian(o, U, c, a, vdummy, gc, NULL);
         else global_gradient(o, u, c, a, gc);
-        if (IS_NS(o)) {
-          ns_minus_flux_matrix(o, F, &u[(c * n + a) * K], gc);
-        } else {
+        if (IS_NS(o)) ns_minus_flux_matrix(o, F, &u[(c * n + a) * K], gc);
+        if (HAS_CELL_NU(o)) {
           double nu[5];
           iso_cell_nu(o, c, nu);
           iso_minus_flux_matrix(F, nu, gc);
@@ -1004,7 +1007,7 @@ void oracle_residual(void *h, double t, const double *column, double *res) {
       if (cs >= 0) {
         int as = o->s_node[f * fq + p];
         flux_upwind(o->riemann, fr, uh, &u[(cs * n + as) * K], fu);
-        if (IS_NS(o) || o->scheme == 6) { /* fr/general.hpp:316-350 */
+        if (IS_NS(o) || HAS_CELL_NU(o)) { /* fr/general.hpp:316-350 */
           const double *us = &u[(cs * n + as) * K];
           double gh_[3][5], gs_[3][5], hh[6][5], hs[6][5], gcm[3][5], ucm[5];
           if (o->klocal) {
@@ -1017,9 +1020,8 @@ void oracle_residual(void *h, double t, const double *column, double *res) {
           }
           ddg_common_gradient(o, o->dist[f * fq + p], fr->a, uh, us, gh_, gs_, hh, hs, gcm);
           for (int k = 0; k < 5; ++k) ucm[k] = (uh[k] + us[k]) / 2;
-          if (IS_NS(o)) {
-            ns_minus_flux_normal(o, fu, ucm, gcm, fr->a);
-          } else { /* property = (holder's + sharer's) / 2, fr/general.hpp:331-335 */
+          if (IS_NS(o)) ns_minus_flux_normal(o, fu, ucm, gcm, fr->a);
+          if (HAS_CELL_NU(o)) { /* property = (holder's + sharer's) / 2, fr/general.hpp:331-335 */
             double nh[5], nsh[5];
             iso_cell_nu(o, ch, nh); iso_cell_nu(o, cs, nsh);
             for (int k = 0; k < 5; ++k) { nh[k] += nsh[k]; nh[k] *= 0.5; }
@@ -1068,14 +1070,16 @@ void oracle_residual(void *h, double t, const double *column, double *res) {
         if (kind == 6) { /* no-slip wall: fr/lobatto.hpp:301-319, fr/general.hpp:460-479; no term at all for
                             inviscid systems (fr/general.hpp:455-459) */
           /* fr::General does not override AddFluxOnNoSlipWalls (fem.hpp:382-383): nothing at all there either */
-          if ((!IS_NS(o) && o->scheme != 6) || IS_GENERAL(o)) continue;
+          if ((!IS_NS(o) && !HAS_CELL_NU(o)) || IS_GENERAL(o)) continue;
           double gh_[3][5];
           boundary_flux(o->riemann, 0, fr, uh, given, fu);
           if (o->klocal) { double vd[5]; local_gradient_hessian(o, U, ch, ah, vd, gh_, NULL); }
           else global_gradient(o, u, ch, ah, gh_);
-          if (IS_NS(o)) {
-            ns_minus_flux_no_slip(o, fu, given, uh, gh_, fr->a, o->beta0 / o->dist[f * fq + p]);
-          } else { /* linear.hpp:85-91: the plain normal flux of the cell's own gradient */
+          if (IS_NS(o)) ns_minus_flux_no_slip(o, fu, given, uh, gh_, fr->a, o->beta0 / o->dist[f * fq + p]);
+          /* viscosity.hpp:132-139 over a diffusive base: MinusViscousFlux(flux, nu, ...) follows, which subtracts the
+             base's normal flux of the unpenalised gradient once more before the artificial one */
+          if (o->scheme == 14) ns_minus_flux_normal(o, fu, uh, gh_, fr->a);
+          if (HAS_CELL_NU(o)) { /* linear.hpp:85-91: the plain normal flux of the cell's own gradient */
             double nu[5];
             iso_cell_nu(o, ch, nu);
             iso_minus_flux_normal(fu, nu, gh_, fr->a);

@@ -162,6 +162,24 @@ def test_c_oracle_isotropic_diffusion_matches_golden(name, degree, riemann):
     assert relerr(o.residual(g["u"], cases.GOLDEN_T), g["residual"]) < TOL
 
 
+@pytest.mark.parametrize("name,degree,riemann", cases.ENERGY_NS_GOLDEN_CASES)
+def test_c_oracle_energy_viscosity_over_navier_stokes_matches_golden(name, degree, riemann):
+    """EnergyBasedViscosity over the Navier-Stokes base (viscosity.hpp:76-139, scheme 14 of the C restatement): the
+    residual with the reference's viscosities, no-slip walls included.  With all viscosities zero it is still not plain
+    Navier-Stokes: on no-slip walls the composition subtracts the base's normal flux twice (viscosity.hpp:132-139)."""
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    o = oc.Oracle(_golden_mesh(g), degree, 14, riemann)
+    cases.apply_viscous_oracle(o)
+    o.set_cell_viscosity(g["nu"])
+    assert relerr(o.residual(g["u"], cases.GOLDEN_T), g["residual"]) < TOL
+    o.set_cell_viscosity(None)
+    ns = oc.Oracle(_golden_mesh(g), degree, 3, riemann)
+    cases.apply_viscous_oracle(ns)
+    a, b = o.residual(g["u"], cases.GOLDEN_T).reshape(-1, 135), ns.residual(g["u"], cases.GOLDEN_T).reshape(-1, 135)
+    differ = np.abs(a - b).max(axis=1) > 0
+    assert 0 < differ.sum() < len(differ)          # the cells on the no-slip walls, and only cells
+
+
 @pytest.mark.parametrize("name,degree,riemann", cases.ENERGY_GOLDEN_CASES)
 def test_c_oracle_energy_based_viscosity_matches_golden(name, degree, riemann):
     """EnergyBasedViscosity: damping matrices, UpdateProperties, the residual with the resulting
